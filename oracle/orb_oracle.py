@@ -1,0 +1,197 @@
+"""ctypes loader for the CPU oracle (oracle/liborb_oracle.so).  TEST INFRASTRUCTURE ONLY.
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs import this
+module; the product package never does.  See oracle/orb_oracle.h for what each function restates.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_SO = os.path.join(_HERE, "liborb_oracle.so")
+
+KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"), ("response", "<f4"),
+                     ("octave", "<i4"), ("class_id", "<i4")])
+MATCH_DTYPE = np.dtype([("best1", "<i4"), ("best2", "<i4"), ("idx", "<i4"), ("accepted", "<i4")])
+
+
+def build(force=False):
+    """Compile the oracle with its Makefile (gcc only; no reference sources are read)."""
+    srcs = [os.path.join(_HERE, f) for f in ("orb_oracle.cpp", "match_oracle.cpp", "orb_oracle.h", "Makefile")]
+    if force or not os.path.exists(_SO) or any(os.path.getmtime(s) > os.path.getmtime(_SO) for s in srcs):
+        subprocess.check_call(["make", "-C", _HERE, "liborb_oracle.so"], stdout=subprocess.DEVNULL)
+    return _SO
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is not None:
+        return _lib
+    build()
+    L = C.CDLL(_SO)
+    u8p, i32p, f32p, vp = C.POINTER(C.c_uint8), C.POINTER(C.c_int32), C.POINTER(C.c_float), C.c_void_p
+    L.orc_extractor_create.restype = vp
+    L.orc_extractor_create.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int]
+    L.orc_extractor_destroy.argtypes = [vp]
+    L.orc_extract.restype = C.c_int
+    L.orc_extract.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp, vp, C.c_int, i32p]
+    L.orc_num_levels.argtypes = [vp]
+    L.orc_scale_factor.restype = C.c_float
+    L.orc_scale_factor.argtypes = [vp, C.c_int]
+    L.orc_features_per_level.argtypes = [vp, C.c_int]
+    L.orc_umax.argtypes = [vp, C.c_int]
+    L.orc_level_size.argtypes = [vp, C.c_int, i32p, i32p]
+    L.orc_pyramid_level.argtypes = [vp, C.c_int, C.c_int, vp]
+    L.orc_blurred_level.argtypes = [vp, C.c_int, vp]
+    L.orc_fast_candidates.argtypes = [vp, C.c_int, vp, C.c_int]
+    L.orc_level_keypoints.argtypes = [vp, C.c_int, vp, C.c_int]
+    L.orc_resize_linear_u8.argtypes = [vp, C.c_int, C.c_int, C.c_int, vp, C.c_int, C.c_int, C.c_int]
+    L.orc_gaussian7_u8.argtypes = [vp, C.c_int, C.c_int, C.c_int, vp, C.c_int]
+    L.orc_fast9_16.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, vp, C.c_int]
+    L.orc_fast_atan2.restype = C.c_float
+    L.orc_fast_atan2.argtypes = [C.c_float, C.c_float]
+    L.orc_descriptor_distance.argtypes = [vp, vp]
+    L.orc_hamming_top2.argtypes = [vp, C.c_int, vp, C.c_int64, C.c_int, C.c_float, C.c_int, vp]
+    L.orc_stereo_match.restype = C.c_int
+    L.orc_stereo_match.argtypes = [vp, vp, vp, vp, C.c_int, vp, vp, C.c_int, C.c_float, C.c_float, C.c_float, vp, vp]
+    L.orc_knn2_ratio.argtypes = [vp, C.c_int, vp, C.c_int, C.c_double, vp, vp, vp]
+    _lib = L
+    return L
+
+
+def _ptr(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+class OracleExtractor:
+    """Mirror of ORB_SLAM3::ORBextractor (include/ORBextractor.h:43-109) over the CPU oracle."""
+
+    def __init__(self, nfeatures=1200, scale_factor=1.2, nlevels=8, ini_th=20, min_th=7):
+        self.L = lib()
+        self.h = self.L.orc_extractor_create(nfeatures, scale_factor, nlevels, ini_th, min_th)
+        if not self.h:
+            raise ValueError("bad extractor parameters")
+        self.nfeatures, self.nlevels = nfeatures, nlevels
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.L.orc_extractor_destroy(self.h)
+            self.h = None
+
+    def __call__(self, image, lapping=(0, 0)):
+        """Returns (monoIndex, keypoints[KP_DTYPE], descriptors[n,32] u8)."""
+        img = np.ascontiguousarray(image, dtype=np.uint8)
+        cap = self.nfeatures * 2 + 64 * self.nlevels
+        kps = np.zeros(cap, KP_DTYPE)
+        desc = np.zeros((cap, 32), np.uint8)
+        n = C.c_int32(0)
+        rows, cols = (img.shape if img.ndim == 2 else (0, 0))
+        mono = self.L.orc_extract(self.h, _ptr(img) if img.size else None, rows, cols, cols, lapping[0], lapping[1],
+                                  _ptr(kps), _ptr(desc), cap, C.byref(n))
+        if mono < 0:
+            return mono, kps[:0], desc[:0]
+        return mono, kps[:n.value].copy(), desc[:n.value].copy()
+
+    def quotas(self):
+        return [self.L.orc_features_per_level(self.h, l) for l in range(self.nlevels)]
+
+    def scale_factors(self):
+        return [self.L.orc_scale_factor(self.h, l) for l in range(self.nlevels)]
+
+    def umax(self):
+        return [self.L.orc_umax(self.h, v) for v in range(16)]
+
+    def level_size(self, level):
+        w, h = C.c_int32(0), C.c_int32(0)
+        self.L.orc_level_size(self.h, level, C.byref(w), C.byref(h))
+        return w.value, h.value
+
+    def pyramid_level(self, level, padded=False):
+        w, h = self.level_size(level)
+        b = 19 if padded else 0
+        out = np.zeros((h + 2 * b, w + 2 * b), np.uint8)
+        self.L.orc_pyramid_level(self.h, level, int(padded), _ptr(out))
+        return out
+
+    def blurred_level(self, level):
+        w, h = self.level_size(level)
+        out = np.zeros((h, w), np.uint8)
+        rc = self.L.orc_blurred_level(self.h, level, _ptr(out))
+        return out if rc == 0 else None
+
+    def fast_candidates(self, level):
+        n = self.L.orc_fast_candidates(self.h, level, None, 0)
+        out = np.zeros(max(n, 1), KP_DTYPE)
+        self.L.orc_fast_candidates(self.h, level, _ptr(out), n)
+        return out[:n]
+
+    def level_keypoints(self, level):
+        n = self.L.orc_level_keypoints(self.h, level, None, 0)
+        out = np.zeros(max(n, 1), KP_DTYPE)
+        self.L.orc_level_keypoints(self.h, level, _ptr(out), n)
+        return out[:n]
+
+
+def resize_linear(src, dw, dh):
+    src = np.ascontiguousarray(src, np.uint8)
+    dst = np.zeros((dh, dw), np.uint8)
+    lib().orc_resize_linear_u8(_ptr(src), src.shape[1], src.shape[0], src.shape[1], _ptr(dst), dw, dh, dw)
+    return dst
+
+
+def gaussian7(src):
+    src = np.ascontiguousarray(src, np.uint8)
+    dst = np.zeros_like(src)
+    lib().orc_gaussian7_u8(_ptr(src), src.shape[1], src.shape[0], src.shape[1], _ptr(dst), src.shape[1])
+    return dst
+
+
+def fast9_16(roi, t):
+    roi = np.ascontiguousarray(roi, np.uint8)
+    cap = roi.size
+    out = np.zeros(max(cap, 1), KP_DTYPE)
+    n = lib().orc_fast9_16(_ptr(roi), roi.shape[1], roi.shape[0], roi.shape[1], t, _ptr(out), cap)
+    return out[:n]
+
+
+def fast_atan2(y, x):
+    return lib().orc_fast_atan2(float(y), float(x))
+
+
+def descriptor_distance(a, b):
+    a = np.ascontiguousarray(a, np.uint8)
+    b = np.ascontiguousarray(b, np.uint8)
+    return lib().orc_descriptor_distance(_ptr(a), _ptr(b))
+
+
+def hamming_top2(q, db, th=50, ratio=0.9, strict_lt=False):
+    q = np.ascontiguousarray(q, np.uint8)
+    db = np.ascontiguousarray(db, np.uint8)
+    out = np.zeros(q.shape[0], MATCH_DTYPE)
+    lib().orc_hamming_top2(_ptr(q), q.shape[0], _ptr(db), db.shape[0], th, ratio, int(strict_lt), _ptr(out))
+    return out
+
+
+def stereo_match(exL, exR, kpsL, descL, kpsR, descR, mbf, minD, maxD):
+    kpsL = np.ascontiguousarray(kpsL); kpsR = np.ascontiguousarray(kpsR)
+    descL = np.ascontiguousarray(descL, np.uint8); descR = np.ascontiguousarray(descR, np.uint8)
+    u = np.zeros(len(kpsL), np.float32)
+    d = np.zeros(len(kpsL), np.float32)
+    kept = lib().orc_stereo_match(exL.h, exR.h, _ptr(kpsL), _ptr(descL), len(kpsL), _ptr(kpsR), _ptr(descR),
+                                  len(kpsR), mbf, minD, maxD, _ptr(u), _ptr(d))
+    return kept, u, d
+
+
+def knn2_ratio(q, t, ratio=0.7):
+    q = np.ascontiguousarray(q, np.uint8)
+    t = np.ascontiguousarray(t, np.uint8)
+    m = np.zeros(q.shape[0], np.int32)
+    d0 = np.zeros(q.shape[0], np.int32)
+    d1 = np.zeros(q.shape[0], np.int32)
+    lib().orc_knn2_ratio(_ptr(q), q.shape[0], _ptr(t), t.shape[0], ratio, _ptr(m), _ptr(d0), _ptr(d1))
+    return m, d0, d1
