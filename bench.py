@@ -1,0 +1,377 @@
+#!/usr/bin/env python3
+"""bench.py — ORB front-end throughput on B200 (BASELINE.json metric: ORB frames/s at 752x480 / 1200 features,
+plus Hamming matches/s), one JSON line on stdout.
+
+Workload (config.workload): BASELINE.json configs[1] — EuRoC-shaped stereo pairs 2x752x480, ORBextractor(1200, 1.2, 8,
+20, 7), left + right extraction followed by Frame::ComputeStereoMatches — batched: one "step" = one pass of the hot
+path over `pairs` stereo pairs per GPU (frames are independent, so N GPUs each take their own pairs: weak scaling,
+no collective).  `value` = frames/s with the images already in HBM; `e2e` = the same through the host-buffer entry
+points (H2D of the images and D2H of keypoints/descriptors/uRight/depth inside the timed region).
+The second north-star metric, Hamming matches/s (config 5: 4096 queries x 2^20 database rows, top-2 + TH_LOW/ratio,
+database sharded over the ranks with an NCCL all-gather + merge), is reported under "hamming".
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--pairs P] [--impl reference]
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+from concurrent.futures import ThreadPoolExecutor
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+W, H = 752, 480
+PARAMS = (1200, 1.2, 8, 20, 7)
+MBF, FX = 47.90639, 435.2047             # Examples/Stereo-Inertial/EuRoC.yaml:9,26
+WORKLOAD = "euroc_stereo_2x752x480_1200feat_extract+ComputeStereoMatches"
+METRIC = "orb_frames_per_sec_752x480_1200feat"
+STAGES = ["pyramid", "fast", "blur", "quadtree", "assemble", "orient_describe", "stereo", "stereo_median"]
+
+
+def level_sizes():
+    s, out = 1.0, []
+    scale = np.float32(1.0)
+    for l in range(PARAMS[2]):
+        inv = np.float32(1.0) / scale
+        out.append((int(np.rint(np.float32(W) * inv)), int(np.rint(np.float32(H) * inv))))
+        scale = np.float32(float(scale) * float(np.float32(PARAMS[1])))
+    return out
+
+
+def algorithmic_bytes(nkp):
+    """SURVEY.md §8d staged model, per image, split per stage (DESIGN.md 'algorithmic bytes')."""
+    lv = level_sizes()
+    px = sum(w * h for w, h in lv)
+    padded = sum((w + 38) * (h + 38) for w, h in lv)
+    src = sum(w * h for w, h in lv[:-1])
+    per = {"pyramid": W * H + padded + src, "fast": px, "blur": 2 * px,
+           "orient_describe": nkp * (961 + 512 + 32 + 28), "quadtree": 0, "assemble": 0}
+    return per, sum(per.values())
+
+
+def gen_pairs(n, seed0, pin):
+    import torch
+    from orb_slam3_detailed_comments_kor_b200 import synth
+    tl = torch.empty((n, H, W), dtype=torch.uint8, pin_memory=pin)
+    tr = torch.empty((n, H, W), dtype=torch.uint8, pin_memory=pin)
+    L, R = tl.numpy(), tr.numpy()
+    with ThreadPoolExecutor(os.cpu_count() or 4) as ex:
+        list(ex.map(lambda i: synth.stereo_pair(seed0 + i, W, H, L[i], R[i]), range(n)))
+    return tl, tr
+
+
+class ClockSampler:
+    """nvidia-smi clocks/throttle reasons sampled while the timed region runs (B200_PROFILING.md recipe)."""
+    Q = "index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown," \
+        "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=lambda: self.lines.extend(self.proc.stdout), daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        self.t.join(timeout=2)
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cpu_oracle_rate(npairs, threads):
+    """The CPU oracle (oracle/liborb_oracle.so) on `npairs` stereo pairs with `threads` host threads, timed the way the
+    reference instruments itself (around extraction and ComputeStereoMatches, src/Frame.cc:116-127,136-144)."""
+    from oracle import orb_oracle as O
+    from orb_slam3_detailed_comments_kor_b200 import synth
+    pairs = [synth.stereo_pair(900000 + i, W, H) for i in range(npairs)]
+    local = threading.local()
+
+    def work(i):
+        if not hasattr(local, "ex"):
+            local.ex = (O.OracleExtractor(*PARAMS), O.OracleExtractor(*PARAMS))
+        exL, exR = local.ex
+        _, kL, dL = exL(pairs[i][0])
+        _, kR, dR = exR(pairs[i][1])
+        O.stereo_match(exL, exR, kL, dL, kR, dR, MBF, 0.0, FX)
+        return len(kL)
+
+    with ThreadPoolExecutor(threads) as ex:
+        list(ex.map(work, range(min(threads, npairs))))           # warm the per-thread extractors
+        t0 = time.perf_counter()
+        list(ex.map(work, range(npairs)))
+        dt = time.perf_counter() - t0
+    return 2 * npairs / dt, dt
+
+
+def cpu_hamming_rate(nq_sample, ndb, threads):
+    from oracle import orb_oracle as O
+    from orb_slam3_detailed_comments_kor_b200 import synth
+    db, q = synth.descriptors(5, ndb, max(nq_sample, threads))
+    chunks = np.array_split(np.arange(nq_sample), threads)
+    t0 = time.perf_counter()
+    with ThreadPoolExecutor(threads) as ex:
+        list(ex.map(lambda c: O.hamming_top2(q[c], db, 50, 0.9, False) if len(c) else None, chunks))
+    dt = time.perf_counter() - t0
+    return nq_sample * ndb / dt, dt
+
+
+def run_reference(args, rank):
+    """--impl reference: the reference's CPU path for this workload.  The reference itself cannot be compiled here
+    (needs OpenCV/Eigen/Pangolin), so this is the oracle port on all host cores."""
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    sample = max(2, cores)
+    for _ in range(args.warmup):
+        cpu_oracle_rate(min(sample, cores), cores)
+    times = []
+    for _ in range(args.steps):
+        _, dt = cpu_oracle_rate(sample, cores)
+        times.append(dt)
+    ms = 1e3 * float(np.mean(times))
+    value = 2 * sample / (ms / 1e3)
+    hv, hdt = cpu_hamming_rate(max(cores, 16), 1 << 20, cores)
+    line = {"metric": METRIC, "value": value, "unit": "frames/s", "impl": "reference", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "pairs_per_step": sample, "threads": cores},
+            "cpu_baseline": {"value": value, "unit": "frames/s", "cores": cores, "kind": "port",
+                             "sample": "%d stereo pairs per step, frame-parallel over %d threads" % (sample, cores)},
+            "e2e": {"value": value, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "hamming": {"value": hv, "unit": "descriptor_pairs/s", "sample": "%d queries x 2^20 rows" % max(cores, 16),
+                        "cores": cores}}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--pairs", type=int, default=256, help="stereo pairs per GPU per step")
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--hamming-queries", type=int, default=4096)
+    ap.add_argument("--hamming-db", type=int, default=1 << 20)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank)
+        return
+
+    import torch
+    import torch.distributed as dist
+    from orb_slam3_detailed_comments_kor_b200 import ORBextractor, DescriptorDatabase, synth
+    from orb_slam3_detailed_comments_kor_b200 import matcher as M
+    from orb_slam3_detailed_comments_kor_b200 import _lib
+    import ctypes as C
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product has no CPU path")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    P = args.pairs
+    hL, hR = gen_pairs(P, rank * 1000003, pin=True)
+    dL, dR = hL.cuda(non_blocking=True), hR.cuda(non_blocking=True)
+    exL = ORBextractor(*PARAMS, width=W, height=H, device=local_rank, max_batch=P)
+    exR = ORBextractor(*PARAMS, width=W, height=H, device=local_rank, max_batch=P)
+    st = torch.cuda.current_stream().cuda_stream
+    L = _lib.lib()
+
+    def step():
+        exL.extract_batch_device(dL.data_ptr(), P, (0, 0), st)
+        exR.extract_batch_device(dR.data_ptr(), P, (0, 0), st)
+        M.compute_stereo_matches(exL, exR, P, MBF, 0.0, FX, st)
+
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        step()
+    e1.record()
+    barrier()
+    ms_step = max_over_ranks(e0.elapsed_time(e1) / args.steps)
+    value = 2 * P * world / (ms_step / 1e3)
+
+    # per-stage device time: the same steps again with the library's CUDA-event brackets switched on
+    for ex in (exL, exR):
+        _lib.check(L.orbfe_set_profiling(ex.handle, 1))
+    for _ in range(args.steps):
+        step()
+    torch.cuda.synchronize()
+    stage_ms = np.zeros(8)
+    launches = C.c_int64(0)
+    for ex in (exL, exR):
+        buf = (C.c_double * 8)()
+        _lib.check(L.orbfe_stage_times(ex.handle, buf, C.byref(launches)))
+        stage_ms += np.array(list(buf))
+        _lib.check(L.orbfe_set_profiling(ex.handle, 0))
+    clocks = sampler.stop()
+    cnt, _ = exL.batch_counts(P)
+    cntR, _ = exR.batch_counts(P)
+    nkp = float(np.mean(np.concatenate([cnt, cntR])))
+    per_stage_bytes, total_bytes = algorithmic_bytes(nkp)
+    stage_ms_per_step = stage_ms / args.steps            # both extractors together: 2P images per step
+    top = int(np.argmax(stage_ms_per_step[:6]))
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except OSError:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    top_bytes = per_stage_bytes[STAGES[top]] * 2 * P
+    achieved = top_bytes / (stage_ms_per_step[top] / 1e3) / 1e9 if stage_ms_per_step[top] > 0 else 0.0
+    roofline = {"bound": "hbm", "kernel": STAGES[top], "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": achieved / peak, "traffic": None,
+                "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured copy)" if peaks else "fallback 6650 GB/s",
+                "algorithmic_bytes_per_launch": top_bytes,
+                "launch_ms": float(stage_ms_per_step[top]),
+                "stage_ms_per_step": {s: float(v) for s, v in zip(STAGES, stage_ms_per_step)},
+                "whole_step": {"algorithmic_bytes_per_frame": total_bytes,
+                               "achieved": total_bytes * 2 * P / (ms_step / 1e3) / 1e9,
+                               "frac": total_bytes * 2 * P / (ms_step / 1e3) / 1e9 / peak}}
+
+    # end to end through the host-buffer entry points (pinned images in, results out)
+    cap = exL.capacity
+    outL = (np.zeros(P, np.int32), np.zeros(P, np.int32), torch.empty((P, cap, 28), dtype=torch.uint8, pin_memory=True).numpy().view(_lib.KP_DTYPE).reshape(P, cap),
+            torch.empty((P, cap, 32), dtype=torch.uint8, pin_memory=True).numpy())
+    outR = (np.zeros(P, np.int32), np.zeros(P, np.int32), torch.empty((P, cap, 28), dtype=torch.uint8, pin_memory=True).numpy().view(_lib.KP_DTYPE).reshape(P, cap),
+            torch.empty((P, cap, 32), dtype=torch.uint8, pin_memory=True).numpy())
+    hu = torch.empty((P, cap), dtype=torch.float32, pin_memory=True).numpy()
+    hd = torch.empty((P, cap), dtype=torch.float32, pin_memory=True).numpy()
+    hLn, hRn = hL.numpy(), hR.numpy()
+
+    def e2e_step():
+        exL.extract_batch_host(hLn, (0, 0), outL)
+        exR.extract_batch_host(hRn, (0, 0), outR)
+        M.compute_stereo_matches(exL, exR, P, MBF, 0.0, FX)
+        _lib.check(L.orbfe_stereo_result_batch(exL.handle, P, _lib.ptr(hu), _lib.ptr(hd), cap))
+
+    for _ in range(2):
+        e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        e2e_step()
+    torch.cuda.synchronize()
+    e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3 / args.steps)
+    barrier()
+    e2e = {"value": 2 * P * world / (e2e_ms / 1e3), "unit": "frames/s", "ms_per_step": e2e_ms,
+           "h2d_bytes_per_step": 2 * P * W * H,
+           "d2h_bytes_per_step": 2 * P * (cap * 60 + 8) + 2 * P * cap * 4}
+
+    # ---- Hamming top-2 (config 5): database sharded over the ranks, NCCL all-gather of the per-shard top-2 + merge
+    nq, ndb = args.hamming_queries, args.hamming_db
+    rows = ndb // world
+    db, q = synth.descriptors(5, ndb, nq)
+    shard = DescriptorDatabase(rows, nq, device=local_rank)
+    shard.set(db[rank * rows:(rank + 1) * rows], index_base=rank * rows)
+    d_q = torch.from_numpy(q).cuda()
+    d_part = torch.zeros((nq, 4), dtype=torch.int32, device="cuda")
+    d_all = torch.zeros((world, nq, 4), dtype=torch.int32, device="cuda")
+    d_out = torch.zeros((nq, 4), dtype=torch.int32, device="cuda")
+
+    def ham_step():
+        if world == 1:
+            shard.top2_device(d_q.data_ptr(), nq, 50, 0.9, False, d_out.data_ptr(), st)
+        else:
+            shard.top2_device(d_q.data_ptr(), nq, 50, 0.9, False, d_part.data_ptr(), st)
+            dist.all_gather_into_tensor(d_all, d_part)
+            M.merge_top2_device(local_rank, d_all.data_ptr(), world, nq, 50, 0.9, False, d_out.data_ptr(), st)
+
+    for _ in range(3):
+        ham_step()
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        ham_step()
+    e1.record()
+    barrier()
+    ham_ms = max_over_ranks(e0.elapsed_time(e1) / args.steps)
+    pairs_s = nq * rows * world / (ham_ms / 1e3)
+    popc_peak = 148 * 16 * float(peaks.get("sm_max_mhz", 1965.0)) * 1e6 / 8.0   # pairs/s/GPU at 8 POPC per pair
+    hamming = {"value": pairs_s, "unit": "descriptor_pairs/s", "ms_per_step": ham_ms, "scaling": "strong",
+               "queries": nq, "db_rows": ndb, "shards": world, "accepted": int(d_out[:, 3].sum().item()),
+               "roofline": {"bound": "int_popc", "achieved": pairs_s / world, "peak": popc_peak, "unit": "pairs/s/GPU",
+                            "frac": pairs_s / world / popc_peak,
+                            "peak_source": "148 SM x 16 POPC/clk x sm_max_mhz / 8 POPC per pair (nominal; SURVEY.md §8d)"}}
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cores = os.cpu_count() or 1
+        sample = max(4 * cores, 16)
+        rate, dt = cpu_oracle_rate(sample, cores)
+        hrate, hdt = cpu_hamming_rate(max(cores, 16), ndb, cores)
+        cpu = {"value": rate, "unit": "frames/s", "cores": cores, "kind": "port",
+               "sample": "%d stereo pairs (%.1f s wall) frame-parallel over %d threads; oracle built -O3 -march=x86-64-v3" % (sample, dt, cores),
+               "hamming": {"value": hrate, "unit": "descriptor_pairs/s", "sample": "%d queries x %d rows (%.1f s wall)" % (max(cores, 16), ndb, hdt)}}
+
+    if rank == 0:
+        line = {"metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+                "config": {"workload": WORKLOAD, "pairs_per_gpu_per_step": P, "frames_per_step": 2 * P * world,
+                           "l2": "inputs_larger_than_L2 (%d MB of images per step per GPU)" % (2 * P * W * H >> 20),
+                           "mean_keypoints_per_frame": nkp, "parallelism": "frames sharded by rank, no collective"},
+                "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
+                "gpu_launches": (2 * (2 * PARAMS[2] + 4) + 2) * args.steps,
+                "hamming": hamming}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

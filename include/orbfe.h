@@ -1,0 +1,174 @@
+/* orbfe.h — C ABI of liborbfe.so: the B200 (sm_100a) ORB front-end.
+ *
+ * This is the drop-in boundary for ORB-SLAM3's data-parallel hot path.  The reference has no FFI of its
+ * own: the boundary is its C++ class surface, so every entry point below names the reference member
+ * function (file:line under /root/reference) whose work it takes over.  The C++ shims in
+ * include/orbfe_shim/ re-declare those classes with the reference's signatures and forward here.
+ *
+ * Conventions: plain pointers and sizes only; every function returns 0 on success or a negative
+ * ORBFE_E_* code (orbfe_last_error() gives the text, per thread); nothing here falls back to the CPU —
+ * if no CUDA device is usable the call fails.  `stream` arguments are cudaStream_t values passed as
+ * void* (NULL = the object's own stream).  "device" pointers must belong to the object's GPU.
+ */
+#ifndef ORBFE_H
+#define ORBFE_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ORBFE_OK 0
+#define ORBFE_E_EMPTY (-1)    /* empty image: ORBextractor::operator() returns -1 (src/ORBextractor.cc:1072-1073) */
+#define ORBFE_E_INVALID (-2)  /* bad argument / unsupported shape */
+#define ORBFE_E_CUDA (-3)     /* CUDA runtime error (text in orbfe_last_error) */
+#define ORBFE_E_CAPACITY (-4) /* caller buffer or object capacity too small */
+#define ORBFE_E_NCCL (-5)
+
+/* Layout-identical to cv::KeyPoint (pt.x, pt.y, size, angle, response, octave, class_id): 28 bytes. */
+typedef struct orbfe_keypoint {
+    float x, y;
+    float size;
+    float angle;
+    float response;
+    int32_t octave;
+    int32_t class_id;
+} orbfe_keypoint;
+
+/* The five constructor arguments of ORBextractor (include/ORBextractor.h:49-50). */
+typedef struct orbfe_params {
+    int32_t nfeatures;
+    float scale_factor;
+    int32_t nlevels;
+    int32_t ini_th_fast;
+    int32_t min_th_fast;
+} orbfe_params;
+
+/* Result of the top-2 Hamming search for one query (src/ORBmatcher.cc:311-375, 870-908). */
+typedef struct orbfe_match {
+    int32_t best1;    /* bestDist1 (256 when the database is empty) */
+    int32_t best2;    /* bestDist2 */
+    int32_t idx;      /* bestIdx, global database row, lowest row on ties; -1 when empty */
+    int32_t accepted; /* 1 iff best1 passes TH_LOW and the nnratio test */
+} orbfe_match;
+
+typedef struct orbfe_extractor orbfe_extractor;
+typedef struct orbfe_matcher orbfe_matcher;
+
+const char* orbfe_last_error(void);
+int orbfe_device_count(void);
+const char* orbfe_version(void);
+
+/* ------------------------------------------------------------------------------------------------ extractor */
+
+/* Replaces ORBextractor::ORBextractor (src/ORBextractor.cc:408-468): scale tables, per-level quotas, umax,
+ * pattern upload — plus everything a GPU needs once: the image shape and the largest batch are fixed here so
+ * that no call below allocates.  width/height are the input image size; max_batch >= 1. */
+int orbfe_extractor_create(const orbfe_params* params, int device, int width, int height, int max_batch,
+                           orbfe_extractor** out);
+void orbfe_extractor_destroy(orbfe_extractor* ex);
+
+/* Getters of ORBextractor (include/ORBextractor.h:61-81): GetLevels, GetScaleFactors, GetInverseScaleFactors,
+ * GetScaleSigmaSquares, GetInverseScaleSigmaSquares; plus mnFeaturesPerLevel and umax for the parity tests. */
+int orbfe_get_levels(const orbfe_extractor* ex);
+int orbfe_get_scale_factors(const orbfe_extractor* ex, float* scale, float* inv_scale, float* sigma2, float* inv_sigma2);
+int orbfe_get_features_per_level(const orbfe_extractor* ex, int32_t* quota);
+int orbfe_get_umax(const orbfe_extractor* ex, int32_t* umax16);
+/* Upper bound of keypoints one frame can return (sum over levels of quota+3, src/ORBextractor.cc:655-735). */
+int orbfe_keypoint_capacity(const orbfe_extractor* ex);
+int orbfe_level_size(const orbfe_extractor* ex, int level, int* width, int* height);
+
+/* Replaces int ORBextractor::operator()(image, mask, keypoints, descriptors, vLappingArea)
+ * (src/ORBextractor.cc:1068-1150) for one host image.  step = bytes per image row.  kps/desc receive *n
+ * entries (desc is n x 32 bytes); *mono_index is the reference's return value.  rows/cols must equal the
+ * shape given at creation.  Returns ORBFE_E_EMPTY for a NULL/0-sized image like the reference's -1. */
+int orbfe_extract(orbfe_extractor* ex, const uint8_t* image, int rows, int cols, size_t step, int lap0, int lap1,
+                  orbfe_keypoint* kps, uint8_t* desc, int cap, int* n, int* mono_index);
+
+/* The same operator() over a batch of frames that already sit in device memory, densely packed
+ * (frame f at d_images + f*rows*cols).  Asynchronous on `stream`; results stay on the device until fetched.
+ * This is the call the roofline numbers are quoted on (frames are independent: SURVEY.md §8e). */
+int orbfe_extract_batch_device(orbfe_extractor* ex, const uint8_t* d_images, int nframes, int lap0, int lap1,
+                               void* stream);
+/* Same, from host memory (pinned or pageable): host->device copy, extraction, device->host copy of the results.
+ * kps: nframes*cap entries, desc: nframes*cap*32 bytes, n / mono_index: nframes ints.  Synchronous. */
+int orbfe_extract_batch_host(orbfe_extractor* ex, const uint8_t* h_images, int nframes, int lap0, int lap1,
+                             orbfe_keypoint* kps, uint8_t* desc, int cap, int32_t* n, int32_t* mono_index);
+/* Fetch what the last batch call left on the device (synchronises the object's stream). */
+int orbfe_batch_counts(orbfe_extractor* ex, int nframes, int32_t* n, int32_t* mono_index);
+int orbfe_batch_result(orbfe_extractor* ex, int frame, orbfe_keypoint* kps, uint8_t* desc, int cap, int* n,
+                       int* mono_index);
+/* Device views of the last batch's results (for callers that keep everything on the GPU):
+ * keypoints[frame*capacity + i], descriptors[(frame*capacity + i)*32], counts[frame], mono[frame]. */
+int orbfe_batch_device_views(orbfe_extractor* ex, const orbfe_keypoint** d_kps, const uint8_t** d_desc,
+                             const int32_t** d_counts, const int32_t** d_mono);
+
+/* Host mirrors of ORBextractor::mvImagePyramid (include/ORBextractor.h:83; read by src/Frame.cc:804,894-909)
+ * and stage-level views used by the parity tests.  padded != 0 returns the (h+38)x(w+38) bordered buffer. */
+int orbfe_pyramid_level(orbfe_extractor* ex, int frame, int level, int padded, uint8_t* dst);
+int orbfe_blurred_level(orbfe_extractor* ex, int frame, int level, uint8_t* dst);
+/* vToDistributeKeys of one level (src/ORBextractor.cc:846-850): x, y (relative to the 16 px border), response. */
+int orbfe_fast_candidates(orbfe_extractor* ex, int frame, int level, orbfe_keypoint* out, int cap, int* n);
+
+/* Per-stage device timing (replaces the REGISTER_TIMES chrono brackets of src/Frame.cc:116-127,136-144): when
+ * enabled, CUDA events on the launch stream bracket every stage; orbfe_stage_times accumulates the finished
+ * launches into ms[8] = {pyramid, fast, blur, quadtree, assemble, orient+describe, stereo match, stereo median}
+ * (adds to the caller's values; synchronises) and returns the number of kernels launched so far in *launches. */
+int orbfe_set_profiling(orbfe_extractor* ex, int enable);
+int orbfe_stage_times(orbfe_extractor* ex, double* ms8, int64_t* launches);
+
+/* --------------------------------------------------------------------------------------------------- stereo */
+
+/* Replaces Frame::ComputeStereoMatches (src/Frame.cc:797-967) for the frames both extractors processed last:
+ * left keypoints/descriptors/pyramids come from exL, right ones from exR (device resident, nothing is
+ * re-uploaded).  minD = 0 and maxD = fx in the reference (maxD must be passed: the reference reads an
+ * uninitialised member, src/Frame.cc:827).  Asynchronous on `stream` (NULL = exL's stream). */
+int orbfe_stereo_match_batch_device(orbfe_extractor* exL, orbfe_extractor* exR, int nframes, float mbf, float minD,
+                                    float maxD, void* stream);
+/* mvuRight / mvDepth of one frame (include/Frame.h:172-173), -1 where unmatched. */
+int orbfe_stereo_result(orbfe_extractor* exL, int frame, float* u_right, float* depth, int cap, int* n);
+/* All frames at once: u_right / depth are nframes*cap floats (row f = frame f). Synchronous. */
+int orbfe_stereo_result_batch(orbfe_extractor* exL, int nframes, float* u_right, float* depth, int cap);
+/* Device views: u_right[frame*capacity + i], depth[...]. */
+int orbfe_stereo_device_views(orbfe_extractor* exL, const float** d_u_right, const float** d_depth);
+
+/* ------------------------------------------------------------------------------------------------- matching */
+
+/* Replaces the distance loop of ORBmatcher::DescriptorDistance (src/ORBmatcher.cc:2591-2607) for n row pairs
+ * held on the host: out[i] = Hamming(a[i], b[i]).  (The one-pair static member itself is an inline in the
+ * shim header: a kernel launch per 32-byte pair would be slower than the eight popcounts.) */
+int orbfe_descriptor_distances(int device, const uint8_t* a, const uint8_t* b, int64_t n, int32_t* out);
+
+/* A database of 256-bit descriptors resident on one GPU + the top-2 search over it: the brute-force core of
+ * ORBmatcher::SearchByBoW (src/ORBmatcher.cc:311-375 `<=TH_LOW`, 870-908 `<TH_LOW`).  index_base is added
+ * to the returned row indices (the shard's first global row). */
+int orbfe_matcher_create(int device, int max_queries, int64_t max_db_rows, orbfe_matcher** out);
+void orbfe_matcher_destroy(orbfe_matcher* m);
+int orbfe_matcher_set_db(orbfe_matcher* m, const uint8_t* h_db, int64_t rows, int64_t index_base);
+int orbfe_matcher_set_db_device(orbfe_matcher* m, const uint8_t* d_db, int64_t rows, int64_t index_base);
+/* Host queries in, host results out (copies inside). th = TH_LOW (50), ratio = mfNNratio, strict_lt selects
+ * `best1 < th` (KF-KF variant) instead of `best1 <= th`. */
+int orbfe_matcher_top2(orbfe_matcher* m, const uint8_t* h_queries, int nq, int th, float ratio, int strict_lt,
+                       orbfe_match* h_out);
+/* Device queries in, device results out, asynchronous on `stream`. */
+int orbfe_matcher_top2_device(orbfe_matcher* m, const uint8_t* d_queries, int nq, int th, float ratio,
+                              int strict_lt, orbfe_match* d_out, void* stream);
+/* Merge step of the sharded database: d_parts holds nshards x nq orbfe_match records (one
+ * block per shard, as gathered over NCCL); writes the global top-2 + acceptance into d_out[nq].  New; the
+ * reference is single-process. */
+int orbfe_top2_merge_device(int device, const orbfe_match* d_parts, int nshards, int nq, int th, float ratio,
+                            int strict_lt, orbfe_match* d_out, void* stream);
+/* One-shot convenience over host memory (creates and destroys a matcher). */
+int orbfe_hamming_top2(int device, const uint8_t* q, int nq, const uint8_t* db, int64_t ndb, int th, float ratio,
+                       int strict_lt, orbfe_match* out);
+
+/* Replaces BFMatcher(NORM_HAMMING).knnMatch(k=2) + the Lowe test `d0 < d1*0.7` evaluated in double of
+ * Frame::ComputeStereoFishEyeMatches (src/Frame.cc:1137-1144).  match[i] = train row or -1; d0/d1 optional. */
+int orbfe_knn2_ratio(int device, const uint8_t* q, int nq, const uint8_t* t, int nt, double ratio, int32_t* match,
+                     int32_t* d0, int32_t* d1);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ORBFE_H */

@@ -164,7 +164,13 @@ void fast9_16(const uint8_t* roi, int w, int h, int step, int t, std::vector<Raw
     std::vector<int> score((size_t)w * h, 0);
     for (int y = 3; y < h - 3; y++)
         for (int x = 3; x < w - 3; x++) {
-            const int m = fast_arc_strength(roi + (ptrdiff_t)y * step + x, step);
+            /* cheap necessary condition first (any 9-arc holds one pixel of each opposite pair), as OpenCV's
+               own early-outs do; the arc strength below decides */
+            const uint8_t* p = roi + (ptrdiff_t)y * step + x;
+            const int hi = p[0] + t, lo = p[0] - t;
+            const int a = p[3 * step], b = p[-3 * step], c = p[3], d = p[-3];
+            if (!(((a > hi || b > hi) && (c > hi || d > hi)) || ((a < lo || b < lo) && (c < lo || d < lo)))) continue;
+            const int m = fast_arc_strength(p, step);
             if (m > t) score[(size_t)y * w + x] = m - 1;
         }
     for (int y = 3; y < h - 3; y++)

@@ -1,0 +1,502 @@
+/* orbfe_host.cu — host side of the extractor part of the C ABI (include/orbfe.h): geometry tables that
+ * ORBextractor::ORBextractor and the per-frame prologues of the reference compute on the CPU
+ * (/root/reference/src/ORBextractor.cc:408-468, 537-545, 763-806, 1152-1160), buffer ownership, copies. */
+#include <math.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <algorithm>
+#include <new>
+
+#include "orbfe_internal.h"
+
+int orbfe_upload_constants(const int* umax16, const int8_t* pattern1024);
+int orbfe_quadtree_smem_bytes(int cap);
+int orbfe_configure_kernels(int quadSmem);
+int orbfe_launch_extract(orbfe_extractor* ex, const uint8_t* d_images, int nframes, int lap0, int lap1, cudaStream_t st);
+int orbfe_collect_stage_times(orbfe_extractor* ex);
+
+static thread_local char g_err[512] = "";
+
+void orbfe_set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof g_err, fmt, ap);
+    va_end(ap);
+}
+
+int orbfe_cuda_fail(cudaError_t e, const char* what) {
+    orbfe_set_error("CUDA error %d (%s) in %s", (int)e, cudaGetErrorString(e), what);
+    return ORBFE_E_CUDA;
+}
+
+static const int8_t kPattern[1024] = {
+#include "../../include/orbfe_pattern31.inc"
+};
+
+static inline int cv_round_f(float v) { return (int)lrintf(v); }
+static inline int cv_round_d(double v) { return (int)lrint(v); }
+static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+/* cv::resize INTER_LINEAR coefficient tables: entry = (source index, c0 | c1 << 16). */
+static void linear_table(int ssize, int dsize, std::vector<uint2>& out) {
+    const double scale = 1.0 / ((double)dsize / ssize);
+    for (int dd = 0; dd < dsize; dd++) {
+        float f = (float)((dd + 0.5) * scale - 0.5);
+        int s = (int)floorf(f);
+        f -= s;
+        if (s < 0) { s = 0; f = 0.f; }
+        if (s >= ssize - 1) { s = ssize - 1; f = 0.f; }
+        const int c0 = cv_round_f((1.f - f) * 2048.f), c1 = cv_round_f(f * 2048.f);
+        out.push_back(make_uint2((unsigned)s, (unsigned)c0 | ((unsigned)c1 << 16)));
+    }
+}
+
+template <typename T>
+static int dev_alloc(orbfe_extractor* ex, T** p, size_t count) {
+    void* v = nullptr;
+    ORBFE_CUDA(cudaMalloc(&v, std::max<size_t>(count, 1) * sizeof(T)));
+    ex->allocs.push_back(v);
+    *p = (T*)v;
+    return 0;
+}
+
+extern "C" {
+
+const char* orbfe_last_error(void) { return g_err; }
+const char* orbfe_version(void) { return "orbfe 0.1 (sm_100a)"; }
+
+int orbfe_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) return 0;
+    return n;
+}
+
+void orbfe_extractor_destroy(orbfe_extractor* ex) {
+    if (!ex) return;
+    cudaSetDevice(ex->device);
+    if (ex->stream) cudaStreamSynchronize(ex->stream);
+    for (void* p : ex->allocs) cudaFree(p);
+    if (ex->hKps) cudaFreeHost(ex->hKps);
+    if (ex->hDesc) cudaFreeHost(ex->hDesc);
+    if (ex->hCount) cudaFreeHost(ex->hCount);
+    if (ex->hMono) cudaFreeHost(ex->hMono);
+    for (cudaEvent_t ev : ex->ev) if (ev) cudaEventDestroy(ev);
+    if (ex->stream) cudaStreamDestroy(ex->stream);
+    delete ex;
+}
+
+int orbfe_extractor_create(const orbfe_params* p, int device, int width, int height, int max_batch, orbfe_extractor** out) {
+    if (!p || !out) { orbfe_set_error("null argument"); return ORBFE_E_INVALID; }
+    *out = nullptr;
+    if (p->nlevels < 1 || p->nlevels > ORBFE_MAX_LEVELS || p->nfeatures < 1 || !(p->scale_factor > 1.0f) || max_batch < 1 ||
+        p->ini_th_fast < 1 || p->min_th_fast < 1 || p->ini_th_fast > 254 || p->min_th_fast > 254) {
+        orbfe_set_error("unsupported extractor parameters");
+        return ORBFE_E_INVALID;
+    }
+    if (width < 1 || height < 1 || width > 4000 || height > 4000) {
+        orbfe_set_error("unsupported image size %dx%d", width, height);
+        return ORBFE_E_INVALID;
+    }
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev) {
+        orbfe_set_error("no usable CUDA device %d (found %d); this library has no CPU path", device, ndev);
+        return ORBFE_E_CUDA;
+    }
+    ORBFE_CUDA(cudaSetDevice(device));
+
+    orbfe_extractor* ex = new (std::nothrow) orbfe_extractor();
+    if (!ex) return ORBFE_E_INVALID;
+    ex->device = device;
+    ex->maxBatch = max_batch;
+    ex->lastBatch = 0;
+    ex->params = *p;
+    ex->stream = nullptr;
+    ex->hKps = nullptr; ex->hDesc = nullptr; ex->hCount = nullptr; ex->hMono = nullptr;
+    ex->profiling = 0; ex->stagePending = 0; ex->stereoPending = 0; ex->launches = 0;
+    memset(ex->ev, 0, sizeof ex->ev);
+    memset(ex->stageMs, 0, sizeof ex->stageMs);
+    memset(&ex->d, 0, sizeof ex->d);
+    memset(&ex->b, 0, sizeof ex->b);
+    const int nl = p->nlevels;
+
+    /* ORBextractor.cc:413-444 — the member scaleFactor is a double initialised from the float argument */
+    const double sf = (double)p->scale_factor;
+    ex->scale.assign(nl, 1.f); ex->sigma2.assign(nl, 1.f);
+    for (int i = 1; i < nl; i++) {
+        ex->scale[i] = (float)(ex->scale[i - 1] * sf);
+        ex->sigma2[i] = ex->scale[i] * ex->scale[i];
+    }
+    ex->invScale.resize(nl); ex->invSigma2.resize(nl);
+    for (int i = 0; i < nl; i++) { ex->invScale[i] = 1.0f / ex->scale[i]; ex->invSigma2[i] = 1.0f / ex->sigma2[i]; }
+    ex->quota.resize(nl);
+    {
+        const float factor = (float)(1.0f / sf);
+        float nDesired = p->nfeatures * (1 - factor) / (1 - (float)pow((double)factor, (double)nl));
+        int sum = 0;
+        for (int l = 0; l < nl - 1; l++) {
+            ex->quota[l] = cv_round_f(nDesired);
+            sum += ex->quota[l];
+            nDesired *= factor;
+        }
+        ex->quota[nl - 1] = std::max(p->nfeatures - sum, 0);
+    }
+    /* ORBextractor.cc:452-467 */
+    ex->umax.assign(16, 0);
+    {
+        int v, v0;
+        const int vmax = (int)floorf(15 * sqrtf(2.f) / 2 + 1), vmin = (int)ceilf(15 * sqrtf(2.f) / 2);
+        for (v = 0; v <= vmax; ++v) ex->umax[v] = cv_round_d(sqrt(225.0 - v * v));
+        for (v = 15, v0 = 0; v >= vmin; --v) {
+            while (ex->umax[v0] == ex->umax[v0 + 1]) ++v0;
+            ex->umax[v] = v0;
+            ++v0;
+        }
+    }
+
+    ExDesc& d = ex->d;
+    d.nlevels = nl; d.W = width; d.H = height; d.iniTh = p->ini_th_fast; d.minTh = p->min_th_fast;
+    std::vector<CellDesc> cells;
+    std::vector<uint2> tabs;
+    size_t pyrOff = 0, blurOff = 0;
+    int keyTotal = 0, selTotal = 0, nodeCap = 64;
+    for (int l = 0; l < nl; l++) {
+        LevelDesc& L = d.lv[l];
+        L.w = cv_round_f((float)width * ex->invScale[l]);  /* ORBextractor.cc:1156-1157 */
+        L.h = cv_round_f((float)height * ex->invScale[l]);
+        const float fw = (float)(L.w - 2 * ORBFE_MIN_BORDER), fh = (float)(L.h - 2 * ORBFE_MIN_BORDER);
+        L.nCols = fw > 0 ? (int)(fw / 35.f) : 0;
+        L.nRows = fh > 0 ? (int)(fh / 35.f) : 0;
+        if (L.nCols < 1 || L.nRows < 1) {
+            orbfe_set_error("level %d is %dx%d: too small for the 35 px FAST grid (ORBextractor.cc:782-785 would divide by zero)", l, L.w, L.h);
+            delete ex;
+            return ORBFE_E_INVALID;
+        }
+        L.wCell = (int)ceilf(fw / L.nCols);
+        L.hCell = (int)ceilf(fh / L.nRows);
+        L.nIni = (int)roundf(fw / (float)(L.h - 2 * ORBFE_MIN_BORDER)); /* ORBextractor.cc:541 */
+        if (L.nIni < 1) {
+            orbfe_set_error("level %d aspect ratio gives 0 initial quadtree nodes (ORBextractor.cc:541)", l);
+            delete ex;
+            return ORBFE_E_INVALID;
+        }
+        L.hX = fw / L.nIni;
+        L.pitch = (int)align_up(ORBFE_ROW_LEAD + L.w + ORBFE_EDGE, 16);
+        L.pyrOff = (int)pyrOff;
+        pyrOff = align_up(pyrOff + (size_t)L.pitch * (L.h + 2 * ORBFE_EDGE), 256);
+        L.bpitch = (int)align_up(L.w, 16);
+        L.blurOff = (int)blurOff;
+        blurOff = align_up(blurOff + (size_t)L.bpitch * L.h, 256);
+        L.quota = ex->quota[l];
+        L.scale = ex->scale[l];
+        L.kpSize = (float)(int)(31 * ex->scale[l]); /* ORBextractor.cc:862 */
+        L.selBase = selTotal;
+        L.selCap = std::max(L.quota + 3, 4 * L.nIni);
+        selTotal += L.selCap;
+        L.cellBase = (int)cells.size();
+        L.keyBase = keyTotal;
+        const int minB = ORBFE_MIN_BORDER, maxBX = L.w - ORBFE_EDGE + 3, maxBY = L.h - ORBFE_EDGE + 3;
+        for (int i = 0; i < L.nRows; i++)
+            for (int j = 0; j < L.nCols; j++) {
+                CellDesc c;
+                memset(&c, 0, sizeof c);
+                const int iniY = minB + i * L.hCell, iniX = minB + j * L.wCell;
+                int maxY = iniY + L.hCell + 6, maxX = iniX + L.wCell + 6;
+                const bool skip = (iniY >= maxBY - 3) || (iniX >= maxBX - 6); /* ORBextractor.cc:792,801 */
+                if (maxY > maxBY) maxY = maxBY;
+                if (maxX > maxBX) maxX = maxBX;
+                c.x0 = (short)iniX; c.y0 = (short)iniY;
+                c.rw = (short)(skip ? 0 : maxX - iniX);
+                c.rh = (short)(skip ? 0 : maxY - iniY);
+                c.level = (short)l;
+                c.xoff = (short)(j * L.wCell); c.yoff = (short)(i * L.hCell);
+                const int cw = std::max(c.rw - 6, 0), ch = std::max(c.rh - 6, 0);
+                c.candBase = keyTotal;
+                c.candCap = ((cw + 1) / 2) * ((ch + 1) / 2); /* NMS survivors are never 8-adjacent */
+                keyTotal += c.candCap;
+                if (c.rw > 76 || c.rh > 76) { orbfe_set_error("internal: cell larger than the FAST tile"); delete ex; return ORBFE_E_INVALID; }
+                cells.push_back(c);
+            }
+        L.keyCap = keyTotal - L.keyBase;
+        nodeCap = std::max(nodeCap, std::max(L.selCap, std::max(L.nIni, L.nCols * L.nRows)));
+        if (l > 0) {
+            L.tabX = (int)tabs.size();
+            linear_table(d.lv[l - 1].w, L.w, tabs);
+            L.tabY = (int)tabs.size();
+            linear_table(d.lv[l - 1].h, L.h, tabs);
+        }
+    }
+    int cap2 = 64;
+    while (cap2 < nodeCap) cap2 <<= 1;
+    if (cap2 > 2048) {
+        orbfe_set_error("nfeatures too large for the on-chip quadtree (node capacity %d > 2048)", cap2);
+        delete ex;
+        return ORBFE_E_INVALID;
+    }
+    d.nodeCap = cap2;
+    d.nCells = (int)cells.size();
+    d.candCap = keyTotal;
+    d.kpCap = selTotal;
+    d.pyrSlab = align_up(pyrOff + 256, 256);
+    d.blurSlab = align_up(blurOff + 256, 256);
+    ex->quadSmem = orbfe_quadtree_smem_bytes(cap2);
+
+    int rc = 0;
+    const size_t B = (size_t)max_batch;
+    ExBuffers& b = ex->b;
+    CellDesc* dCells = nullptr;
+    uint2* dTabs = nullptr;
+#define TRY(x) do { rc = (x); if (rc) { orbfe_extractor_destroy(ex); return rc; } } while (0)
+#define TRYC(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { rc = orbfe_cuda_fail(e_, #x); orbfe_extractor_destroy(ex); return rc; } } while (0)
+    TRYC(cudaStreamCreateWithFlags(&ex->stream, cudaStreamNonBlocking));
+    for (cudaEvent_t& ev : ex->ev) TRYC(cudaEventCreate(&ev));
+    TRY(dev_alloc(ex, &b.pyr, B * d.pyrSlab + 256));
+    TRY(dev_alloc(ex, &b.blur, B * d.blurSlab + 256));
+    TRY(dev_alloc(ex, &b.cand, B * d.candCap));
+    TRY(dev_alloc(ex, &b.cellCount, B * d.nCells));
+    TRY(dev_alloc(ex, &b.keys, B * d.candCap));
+    TRY(dev_alloc(ex, &b.keyNode, B * d.candCap));
+    TRY(dev_alloc(ex, &b.sel, B * d.kpCap));
+    TRY(dev_alloc(ex, &b.selCount, B * nl));
+    TRY(dev_alloc(ex, &b.work, B * d.kpCap));
+    TRY(dev_alloc(ex, &b.kps, B * d.kpCap));
+    TRY(dev_alloc(ex, &b.desc, B * d.kpCap * 32));
+    TRY(dev_alloc(ex, &b.count, B));
+    TRY(dev_alloc(ex, &b.mono, B));
+    TRY(dev_alloc(ex, &b.uRight, B * d.kpCap));
+    TRY(dev_alloc(ex, &b.depth, B * d.kpCap));
+    TRY(dev_alloc(ex, &b.sadBest, B * d.kpCap));
+    TRY(dev_alloc(ex, &dCells, cells.size()));
+    TRY(dev_alloc(ex, &dTabs, tabs.size()));
+    TRY(dev_alloc(ex, &ex->inputStage, B * (size_t)width * height));
+    b.cells = dCells;
+    b.tabs = dTabs;
+    b.input = ex->inputStage;
+    TRYC(cudaMemcpy(dCells, cells.data(), cells.size() * sizeof(CellDesc), cudaMemcpyHostToDevice));
+    if (!tabs.empty()) TRYC(cudaMemcpy(dTabs, tabs.data(), tabs.size() * sizeof(uint2), cudaMemcpyHostToDevice));
+    TRYC(cudaMemset(b.pyr, 0, B * d.pyrSlab + 256));
+    TRYC(cudaMemset(b.blur, 0, B * d.blurSlab + 256));
+    TRYC(cudaMemset(b.count, 0, B * sizeof(int)));
+    TRYC(cudaMemset(b.mono, 0, B * sizeof(int)));
+    TRYC(cudaMallocHost((void**)&ex->hKps, B * d.kpCap * sizeof(orbfe_keypoint)));
+    TRYC(cudaMallocHost((void**)&ex->hDesc, B * d.kpCap * 32));
+    TRYC(cudaMallocHost((void**)&ex->hCount, B * sizeof(int)));
+    TRYC(cudaMallocHost((void**)&ex->hMono, B * sizeof(int)));
+    TRY(orbfe_upload_constants(ex->umax.data(), kPattern));
+    TRY(orbfe_configure_kernels(ex->quadSmem));
+#undef TRY
+#undef TRYC
+    *out = ex;
+    return ORBFE_OK;
+}
+
+int orbfe_set_profiling(orbfe_extractor* ex, int enable) {
+    if (!ex) return ORBFE_E_INVALID;
+    ORBFE_CUDA(cudaSetDevice(ex->device));
+    if (!enable && (ex->stagePending || ex->stereoPending)) { int rc = orbfe_collect_stage_times(ex); if (rc) return rc; }
+    ex->profiling = enable ? 1 : 0;
+    return ORBFE_OK;
+}
+
+int orbfe_stage_times(orbfe_extractor* ex, double* ms8, int64_t* launches) {
+    if (!ex) return ORBFE_E_INVALID;
+    ORBFE_CUDA(cudaSetDevice(ex->device));
+    int rc = orbfe_collect_stage_times(ex);
+    if (rc) return rc;
+    if (ms8) for (int i = 0; i < ORBFE_NUM_STAGES + 2; i++) { ms8[i] += ex->stageMs[i]; ex->stageMs[i] = 0.0; }
+    if (launches) *launches = ex->launches;
+    return ORBFE_OK;
+}
+
+int orbfe_get_levels(const orbfe_extractor* ex) { return ex ? ex->d.nlevels : ORBFE_E_INVALID; }
+
+int orbfe_get_scale_factors(const orbfe_extractor* ex, float* s, float* is, float* s2, float* is2) {
+    if (!ex) return ORBFE_E_INVALID;
+    for (int i = 0; i < ex->d.nlevels; i++) {
+        if (s) s[i] = ex->scale[i];
+        if (is) is[i] = ex->invScale[i];
+        if (s2) s2[i] = ex->sigma2[i];
+        if (is2) is2[i] = ex->invSigma2[i];
+    }
+    return ORBFE_OK;
+}
+
+int orbfe_get_features_per_level(const orbfe_extractor* ex, int32_t* q) {
+    if (!ex || !q) return ORBFE_E_INVALID;
+    for (int i = 0; i < ex->d.nlevels; i++) q[i] = ex->quota[i];
+    return ORBFE_OK;
+}
+
+int orbfe_get_umax(const orbfe_extractor* ex, int32_t* u) {
+    if (!ex || !u) return ORBFE_E_INVALID;
+    for (int i = 0; i < 16; i++) u[i] = ex->umax[i];
+    return ORBFE_OK;
+}
+
+int orbfe_keypoint_capacity(const orbfe_extractor* ex) { return ex ? ex->d.kpCap : ORBFE_E_INVALID; }
+
+int orbfe_level_size(const orbfe_extractor* ex, int level, int* w, int* h) {
+    if (!ex || level < 0 || level >= ex->d.nlevels) return ORBFE_E_INVALID;
+    if (w) *w = ex->d.lv[level].w;
+    if (h) *h = ex->d.lv[level].h;
+    return ORBFE_OK;
+}
+
+int orbfe_extract_batch_device(orbfe_extractor* ex, const uint8_t* d_images, int nframes, int lap0, int lap1, void* stream) {
+    if (!ex || !d_images) { orbfe_set_error("null argument"); return ORBFE_E_INVALID; }
+    if (nframes < 1 || nframes > ex->maxBatch) {
+        orbfe_set_error("nframes %d outside [1, max_batch=%d]", nframes, ex->maxBatch);
+        return ORBFE_E_CAPACITY;
+    }
+    ORBFE_CUDA(cudaSetDevice(ex->device));
+    ex->lastBatch = nframes;
+    return orbfe_launch_extract(ex, d_images, nframes, lap0, lap1, stream ? (cudaStream_t)stream : ex->stream);
+}
+
+int orbfe_batch_counts(orbfe_extractor* ex, int nframes, int32_t* n, int32_t* mono) {
+    if (!ex || nframes < 1 || nframes > ex->lastBatch) { orbfe_set_error("bad frame count"); return ORBFE_E_INVALID; }
+    ORBFE_CUDA(cudaSetDevice(ex->device));
+    ORBFE_CUDA(cudaDeviceSynchronize());
+    if (n) ORBFE_CUDA(cudaMemcpy(n, ex->b.count, nframes * sizeof(int), cudaMemcpyDeviceToHost));
+    if (mono) ORBFE_CUDA(cudaMemcpy(mono, ex->b.mono, nframes * sizeof(int), cudaMemcpyDeviceToHost));
+    return ORBFE_OK;
+}
+
+int orbfe_batch_result(orbfe_extractor* ex, int frame, orbfe_keypoint* kps, uint8_t* desc, int cap, int* n, int* mono) {
+    if (!ex || frame < 0 || frame >= ex->lastBatch) { orbfe_set_error("bad frame index"); return ORBFE_E_INVALID; }
+    ORBFE_CUDA(cudaSetDevice(ex->device));
+    ORBFE_CUDA(cudaDeviceSynchronize());
+    int cnt = 0, mi = 0;
+    ORBFE_CUDA(cudaMemcpy(&cnt, ex->b.count + frame, sizeof(int), cudaMemcpyDeviceToHost));
+    ORBFE_CUDA(cudaMemcpy(&mi, ex->b.mono + frame, sizeof(int), cudaMemcpyDeviceToHost));
+    if (n) *n = cnt;
+    if (mono) *mono = mi;
+    if (cnt > cap) { orbfe_set_error("caller capacity %d < %d keypoints", cap, cnt); return ORBFE_E_CAPACITY; }
+    if (kps && cnt) ORBFE_CUDA(cudaMemcpy(kps, ex->b.kps + (size_t)frame * ex->d.kpCap, (size_t)cnt * sizeof(orbfe_keypoint), cudaMemcpyDeviceToHost));
+    if (desc && cnt) ORBFE_CUDA(cudaMemcpy(desc, ex->b.desc + (size_t)frame * ex->d.kpCap * 32, (size_t)cnt * 32, cudaMemcpyDeviceToHost));
+    return ORBFE_OK;
+}
+
+int orbfe_batch_device_views(orbfe_extractor* ex, const orbfe_keypoint** k, const uint8_t** de, const int32_t** c, const int32_t** m) {
+    if (!ex) return ORBFE_E_INVALID;
+    if (k) *k = ex->b.kps;
+    if (de) *de = ex->b.desc;
+    if (c) *c = ex->b.count;
+    if (m) *m = ex->b.mono;
+    return ORBFE_OK;
+}
+
+int orbfe_extract_batch_host(orbfe_extractor* ex, const uint8_t* h_images, int nframes, int lap0, int lap1,
+                             orbfe_keypoint* kps, uint8_t* desc, int cap, int32_t* n, int32_t* mono) {
+    if (!ex || !h_images) { orbfe_set_error("null argument"); return ORBFE_E_INVALID; }
+    if (nframes < 1 || nframes > ex->maxBatch) { orbfe_set_error("nframes %d outside [1, max_batch=%d]", nframes, ex->maxBatch); return ORBFE_E_CAPACITY; }
+    ORBFE_CUDA(cudaSetDevice(ex->device));
+    const size_t frameBytes = (size_t)ex->d.W * ex->d.H;
+    cudaStream_t st = ex->stream;
+    ORBFE_CUDA(cudaMemcpyAsync(ex->inputStage, h_images, frameBytes * nframes, cudaMemcpyHostToDevice, st));
+    ex->lastBatch = nframes;
+    int rc = orbfe_launch_extract(ex, ex->inputStage, nframes, lap0, lap1, st);
+    if (rc) return rc;
+    const int kc = ex->d.kpCap;
+    ORBFE_CUDA(cudaMemcpyAsync(ex->hCount, ex->b.count, nframes * sizeof(int), cudaMemcpyDeviceToHost, st));
+    ORBFE_CUDA(cudaMemcpyAsync(ex->hMono, ex->b.mono, nframes * sizeof(int), cudaMemcpyDeviceToHost, st));
+    if (cap >= kc) {
+        /* caller rows are at least as wide as ours: one strided copy each straight into the caller's arrays */
+        if (kps) ORBFE_CUDA(cudaMemcpy2DAsync(kps, (size_t)cap * sizeof(orbfe_keypoint), ex->b.kps, (size_t)kc * sizeof(orbfe_keypoint),
+                                             (size_t)kc * sizeof(orbfe_keypoint), nframes, cudaMemcpyDeviceToHost, st));
+        if (desc) ORBFE_CUDA(cudaMemcpy2DAsync(desc, (size_t)cap * 32, ex->b.desc, (size_t)kc * 32, (size_t)kc * 32, nframes, cudaMemcpyDeviceToHost, st));
+        ORBFE_CUDA(cudaStreamSynchronize(st));
+    } else {
+        if (kps) ORBFE_CUDA(cudaMemcpyAsync(ex->hKps, ex->b.kps, (size_t)nframes * kc * sizeof(orbfe_keypoint), cudaMemcpyDeviceToHost, st));
+        if (desc) ORBFE_CUDA(cudaMemcpyAsync(ex->hDesc, ex->b.desc, (size_t)nframes * kc * 32, cudaMemcpyDeviceToHost, st));
+        ORBFE_CUDA(cudaStreamSynchronize(st));
+        for (int f = 0; f < nframes; f++) {
+            if (ex->hCount[f] > cap) { orbfe_set_error("caller capacity %d < %d keypoints (frame %d)", cap, ex->hCount[f], f); return ORBFE_E_CAPACITY; }
+            if (kps) memcpy(kps + (size_t)f * cap, ex->hKps + (size_t)f * kc, (size_t)ex->hCount[f] * sizeof(orbfe_keypoint));
+            if (desc) memcpy(desc + (size_t)f * cap * 32, ex->hDesc + (size_t)f * kc * 32, (size_t)ex->hCount[f] * 32);
+        }
+    }
+    for (int f = 0; f < nframes; f++) {
+        if (n) n[f] = ex->hCount[f];
+        if (mono) mono[f] = ex->hMono[f];
+    }
+    return ORBFE_OK;
+}
+
+int orbfe_extract(orbfe_extractor* ex, const uint8_t* image, int rows, int cols, size_t step, int lap0, int lap1,
+                  orbfe_keypoint* kps, uint8_t* desc, int cap, int* n, int* mono_index) {
+    if (n) *n = 0;
+    if (mono_index) *mono_index = -1;
+    if (!ex) { orbfe_set_error("null extractor"); return ORBFE_E_INVALID; }
+    if (!image || rows <= 0 || cols <= 0) { orbfe_set_error("empty image"); return ORBFE_E_EMPTY; }
+    if (rows != ex->d.H || cols != ex->d.W || step < (size_t)cols) {
+        orbfe_set_error("image %dx%d does not match the extractor shape %dx%d", cols, rows, ex->d.W, ex->d.H);
+        return ORBFE_E_INVALID;
+    }
+    ORBFE_CUDA(cudaSetDevice(ex->device));
+    cudaStream_t st = ex->stream;
+    ORBFE_CUDA(cudaMemcpy2DAsync(ex->inputStage, cols, image, step, cols, rows, cudaMemcpyHostToDevice, st));
+    ex->lastBatch = 1;
+    int rc = orbfe_launch_extract(ex, ex->inputStage, 1, lap0, lap1, st);
+    if (rc) return rc;
+    ORBFE_CUDA(cudaMemcpyAsync(ex->hCount, ex->b.count, sizeof(int), cudaMemcpyDeviceToHost, st));
+    ORBFE_CUDA(cudaMemcpyAsync(ex->hMono, ex->b.mono, sizeof(int), cudaMemcpyDeviceToHost, st));
+    ORBFE_CUDA(cudaMemcpyAsync(ex->hKps, ex->b.kps, (size_t)ex->d.kpCap * sizeof(orbfe_keypoint), cudaMemcpyDeviceToHost, st));
+    ORBFE_CUDA(cudaMemcpyAsync(ex->hDesc, ex->b.desc, (size_t)ex->d.kpCap * 32, cudaMemcpyDeviceToHost, st));
+    ORBFE_CUDA(cudaStreamSynchronize(st));
+    const int cnt = ex->hCount[0];
+    if (n) *n = cnt;
+    if (mono_index) *mono_index = ex->hMono[0];
+    if (cnt > cap) { orbfe_set_error("caller capacity %d < %d keypoints", cap, cnt); return ORBFE_E_CAPACITY; }
+    if (kps) memcpy(kps, ex->hKps, (size_t)cnt * sizeof(orbfe_keypoint));
+    if (desc) memcpy(desc, ex->hDesc, (size_t)cnt * 32);
+    return ORBFE_OK;
+}
+
+int orbfe_pyramid_level(orbfe_extractor* ex, int frame, int level, int padded, uint8_t* dst) {
+    if (!ex || !dst || level < 0 || level >= ex->d.nlevels || frame < 0 || frame >= ex->maxBatch) return ORBFE_E_INVALID;
+    ORBFE_CUDA(cudaSetDevice(ex->device));
+    ORBFE_CUDA(cudaDeviceSynchronize());
+    const LevelDesc& L = ex->d.lv[level];
+    const int B = padded ? ORBFE_EDGE : 0;
+    const uint8_t* src = ex->b.pyr + (size_t)frame * ex->d.pyrSlab + L.pyrOff + (size_t)(ORBFE_EDGE - B) * L.pitch + ORBFE_ROW_LEAD - B;
+    ORBFE_CUDA(cudaMemcpy2D(dst, L.w + 2 * B, src, L.pitch, L.w + 2 * B, L.h + 2 * B, cudaMemcpyDeviceToHost));
+    return ORBFE_OK;
+}
+
+int orbfe_blurred_level(orbfe_extractor* ex, int frame, int level, uint8_t* dst) {
+    if (!ex || !dst || level < 0 || level >= ex->d.nlevels || frame < 0 || frame >= ex->maxBatch) return ORBFE_E_INVALID;
+    ORBFE_CUDA(cudaSetDevice(ex->device));
+    ORBFE_CUDA(cudaDeviceSynchronize());
+    const LevelDesc& L = ex->d.lv[level];
+    ORBFE_CUDA(cudaMemcpy2D(dst, L.w, ex->b.blur + (size_t)frame * ex->d.blurSlab + L.blurOff, L.bpitch, L.w, L.h, cudaMemcpyDeviceToHost));
+    return ORBFE_OK;
+}
+
+int orbfe_fast_candidates(orbfe_extractor* ex, int frame, int level, orbfe_keypoint* out, int cap, int* n) {
+    if (!ex || level < 0 || level >= ex->d.nlevels || frame < 0 || frame >= ex->maxBatch) return ORBFE_E_INVALID;
+    ORBFE_CUDA(cudaSetDevice(ex->device));
+    ORBFE_CUDA(cudaDeviceSynchronize());
+    const LevelDesc& L = ex->d.lv[level];
+    const int ncell = L.nCols * L.nRows;
+    std::vector<int> counts(ncell);
+    std::vector<CellDesc> cells(ncell);
+    ORBFE_CUDA(cudaMemcpy(counts.data(), ex->b.cellCount + (size_t)frame * ex->d.nCells + L.cellBase, ncell * sizeof(int), cudaMemcpyDeviceToHost));
+    ORBFE_CUDA(cudaMemcpy(cells.data(), ex->b.cells + L.cellBase, ncell * sizeof(CellDesc), cudaMemcpyDeviceToHost));
+    std::vector<uint32_t> keys(std::max(L.keyCap, 1));
+    ORBFE_CUDA(cudaMemcpy(keys.data(), ex->b.cand + (size_t)frame * ex->d.candCap + L.keyBase, (size_t)L.keyCap * 4, cudaMemcpyDeviceToHost));
+    int total = 0;
+    for (int c = 0; c < ncell; c++)
+        for (int i = 0; i < counts[c]; i++, total++) {
+            if (!out || total >= cap) continue;
+            const uint32_t p = keys[cells[c].candBase - L.keyBase + i];
+            orbfe_keypoint& o = out[total];
+            o.x = (float)(p & 0xFFF); o.y = (float)((p >> 12) & 0xFFF); o.size = 7.f; o.angle = -1.f;
+            o.response = (float)(p >> 24); o.octave = 0; o.class_id = -1;
+        }
+    if (n) *n = total;
+    return ORBFE_OK;
+}
+
+}  /* extern "C" */

@@ -1,0 +1,119 @@
+/* orbfe_internal.h — shared declarations of liborbfe.so (not installed; the public surface is include/orbfe.h). */
+#ifndef ORBFE_INTERNAL_H
+#define ORBFE_INTERNAL_H
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string>
+#include <vector>
+
+#include "../../include/orbfe.h"
+
+#define ORBFE_MAX_LEVELS 16
+#define ORBFE_EDGE 19        /* EDGE_THRESHOLD, src/ORBextractor.cc:72 */
+#define ORBFE_MIN_BORDER 16  /* EDGE_THRESHOLD-3, src/ORBextractor.cc:771 */
+#define ORBFE_NUM_STAGES 6   /* pyramid, fast, blur, quadtree, assemble, orient+describe (+2 stereo) */
+#define ORBFE_ROW_LEAD 32    /* byte of a padded row where interior x = 0 sits (16-byte aligned) */
+
+/* Geometry of one pyramid level; identical for every frame of a batch. */
+struct LevelDesc {
+    int w, h;        /* interior size */
+    int pitch;       /* bytes per padded row; padded x=-19 is byte ORBFE_ROW_LEAD-19 */
+    int pyrOff;      /* byte offset of padded row y=-19 inside a frame's pyramid slab */
+    int bpitch;      /* bytes per row of the blurred level (unpadded) */
+    int blurOff;     /* byte offset inside a frame's blur slab */
+    int nCols, nRows, wCell, hCell; /* FAST cell grid, src/ORBextractor.cc:782-785 */
+    int cellBase;    /* first cell of this level in the per-frame cell table */
+    int keyBase;     /* first candidate slot of this level in the per-frame candidate array */
+    int keyCap;      /* candidate slots of this level */
+    int quota;       /* mnFeaturesPerLevel[level] */
+    int nIni;        /* initial quadtree nodes, src/ORBextractor.cc:541 */
+    float hX;        /* src/ORBextractor.cc:543 */
+    int selBase;     /* first selected-keypoint slot of this level in the per-frame arrays */
+    int selCap;      /* max keypoints the quadtree can return for this level */
+    int tabX, tabY;  /* resize coefficient tables (uint2 entries) for producing this level from level-1 */
+    float scale;     /* mvScaleFactor[level] */
+    float kpSize;    /* (float)(int)(31*scale), src/ORBextractor.cc:862 */
+};
+
+struct ExDesc {
+    int nlevels;
+    int W, H;
+    int nCells;       /* cells per frame, all levels */
+    int candCap;      /* candidate slots per frame, all levels */
+    int kpCap;        /* selected keypoints per frame, all levels (= sum selCap) */
+    int nodeCap;      /* quadtree node capacity (max over levels of selCap, padded) */
+    int iniTh, minTh;
+    size_t pyrSlab;   /* bytes per frame */
+    size_t blurSlab;
+    LevelDesc lv[ORBFE_MAX_LEVELS];
+};
+
+/* One FAST cell (src/ORBextractor.cc:787-854): ROI origin in level coordinates and clipped size. */
+struct CellDesc {
+    short x0, y0;     /* iniX, iniY */
+    short rw, rh;     /* maxX-iniX, maxY-iniY (0 when the reference skips the cell) */
+    short level;
+    short xoff, yoff; /* j*wCell, i*hCell added to the keypoint coordinates */
+    short pad;
+    int candBase;     /* first candidate slot of this cell (per frame) */
+    int candCap;
+};
+
+/* Per-frame device buffers, all sized for max_batch at creation. */
+struct ExBuffers {
+    uint8_t* pyr;        /* [B][pyrSlab] */
+    uint8_t* blur;       /* [B][blurSlab] */
+    uint32_t* cand;      /* [B][candCap]  packed x | y<<12 | score<<24, coordinates relative to minBorder */
+    int* cellCount;      /* [B][nCells] */
+    uint32_t* keys;      /* [B][candCap]  quadtree scratch: a level's candidates gathered in cell order */
+    uint16_t* keyNode;   /* [B][candCap]  quadtree scratch: node of each candidate */
+    uint32_t* sel;       /* [B][kpCap]    quadtree output, packed like cand, per level at selBase */
+    int* selCount;       /* [B][nlevels] */
+    uint2* work;         /* [B][kpCap]    (x | y<<16 in level coords, level | slot<<8) in level order */
+    orbfe_keypoint* kps; /* [B][kpCap] */
+    uint8_t* desc;       /* [B][kpCap][32] */
+    int* count;          /* [B] */
+    int* mono;           /* [B] */
+    float* uRight;       /* [B][kpCap] */
+    float* depth;        /* [B][kpCap] */
+    int* sadBest;        /* [B][kpCap] stereo scratch: best SAD per left keypoint, -1 = no match */
+    const CellDesc* cells;
+    const uint2* tabs;   /* resize tables */
+    const uint8_t* input; /* [B][H*W] staging for host-image entry points */
+};
+
+struct orbfe_extractor {
+    int device;
+    int maxBatch;
+    int lastBatch;
+    orbfe_params params;
+    ExDesc d;
+    ExBuffers b;
+    uint8_t* inputStage;  /* device copy of host images */
+    cudaStream_t stream;
+    std::vector<float> scale, invScale, sigma2, invSigma2;
+    std::vector<int> quota, umax;
+    std::vector<void*> allocs;
+    int fastSmem, quadSmem;
+    /* optional per-stage timing (orbfe_set_profiling): events bracket each stage of the last launch */
+    int profiling;
+    cudaEvent_t ev[ORBFE_NUM_STAGES + 3];
+    double stageMs[ORBFE_NUM_STAGES + 2];
+    int stagePending, stereoPending;
+    long long launches;   /* kernels launched so far by this object */
+    /* pinned host staging for the host entry points */
+    orbfe_keypoint* hKps;
+    uint8_t* hDesc;
+    int* hCount;
+    int* hMono;
+};
+
+void orbfe_set_error(const char* fmt, ...);
+int orbfe_cuda_fail(cudaError_t e, const char* what);
+#define ORBFE_CUDA(call)                                          \
+    do {                                                          \
+        cudaError_t e__ = (call);                                 \
+        if (e__ != cudaSuccess) return orbfe_cuda_fail(e__, #call); \
+    } while (0)
+
+#endif

@@ -1,0 +1,534 @@
+/* orbfe_match.cu — sm_100a kernels + C ABI of the descriptor-matching core.
+ *
+ *  k_top2_partial / k_top2_merge   top-2 Hamming search, /root/reference/src/ORBmatcher.cc:311-375, 870-908
+ *                                  (distance = ORBmatcher::DescriptorDistance, :2591-2607); also serves
+ *                                  BFMatcher::knnMatch(k=2) + Lowe test of src/Frame.cc:1137-1144
+ *  k_stereo_match / k_stereo_median Frame::ComputeStereoMatches, src/Frame.cc:797-967
+ *
+ * The Hamming work is XOR + POPC on the integer pipe (8 x 32-bit per 256-bit pair); it is deliberately not
+ * reshaped into a tensor-core contraction (BASELINE.json north_star). */
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string.h>
+
+#include <algorithm>
+#include <new>
+
+#include "orbfe_internal.h"
+
+int orbfe_collect_stage_times(orbfe_extractor* ex);
+
+/* ------------------------------------------------------------------------------------------ top-2 search */
+#define T2_NT 256
+#define T2_QPT 4                    /* queries held in registers per thread */
+#define T2_QTILE (T2_NT * T2_QPT)   /* queries per CTA */
+#define T2_CHUNK 256                /* database rows per shared-memory stage (8 KB) */
+
+static __device__ __forceinline__ int ham256(const uint32_t (&q)[8], const uint4 a, const uint4 b) {
+    return __popc(q[0] ^ a.x) + __popc(q[1] ^ a.y) + __popc(q[2] ^ a.z) + __popc(q[3] ^ a.w) +
+           __popc(q[4] ^ b.x) + __popc(q[5] ^ b.y) + __popc(q[6] ^ b.z) + __popc(q[7] ^ b.w);
+}
+
+static __device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
+    const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(s), "l"(gmem));
+}
+static __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::); }
+template <int N>
+static __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N)); }
+
+/* grid = (query tiles, database slices).  Each thread keeps T2_QPT queries in registers and scans its CTA's
+ * slice, streamed through a double-buffered cp.async stage that the whole CTA reads by broadcast.
+ * Scan order inside a thread is ascending row, so strict `<` keeps the lowest row on ties, exactly like the
+ * reference's sequential loop.  Output: one orbfe_match per (slice, query) in `parts` (idx is global). */
+__global__ void __launch_bounds__(T2_NT) k_top2_partial(const uint4* __restrict__ q, int nq, const uint4* __restrict__ db,
+                                                        long long ndb, long long indexBase, int rowsPerSlice, int initDist,
+                                                        orbfe_match* __restrict__ parts) {
+    __shared__ __align__(16) uint4 s_db[2][T2_CHUNK * 2];
+    const int slice = blockIdx.y;
+    const long long r0 = (long long)slice * rowsPerSlice;
+    const int nrows = (int)max(0LL, min((long long)rowsPerSlice, ndb - r0));
+    uint32_t qr[T2_QPT][8];
+    int b1[T2_QPT], b2[T2_QPT], bi[T2_QPT];
+#pragma unroll
+    for (int i = 0; i < T2_QPT; i++) {
+        const int qi = blockIdx.x * T2_QTILE + i * T2_NT + threadIdx.x;
+        uint4 a = make_uint4(0, 0, 0, 0), b = a;
+        if (qi < nq) { a = __ldg(q + 2 * (size_t)qi); b = __ldg(q + 2 * (size_t)qi + 1); }
+        qr[i][0] = a.x; qr[i][1] = a.y; qr[i][2] = a.z; qr[i][3] = a.w;
+        qr[i][4] = b.x; qr[i][5] = b.y; qr[i][6] = b.z; qr[i][7] = b.w;
+        b1[i] = initDist; b2[i] = initDist; bi[i] = -1;
+    }
+    const uint4* src = db + 2 * r0;
+    const int nchunks = (nrows + T2_CHUNK - 1) / T2_CHUNK;
+    auto stage = [&](int c, int buf) {
+        const int base = c * T2_CHUNK * 2;               /* uint4 index inside the slice */
+        const int lim = nrows * 2;
+        for (int i = threadIdx.x; i < T2_CHUNK * 2; i += T2_NT)
+            if (base + i < lim) cp_async16(&s_db[buf][i], src + base + i);
+        cp_async_commit();
+    };
+    if (nchunks > 0) stage(0, 0);
+    for (int c = 0; c < nchunks; c++) {
+        if (c + 1 < nchunks) { stage(c + 1, (c + 1) & 1); cp_async_wait<1>(); }
+        else cp_async_wait<0>();
+        __syncthreads();
+        const uint4* s = s_db[c & 1];
+        const int rows = min(T2_CHUNK, nrows - c * T2_CHUNK);
+        const int rowBase = (int)(indexBase + r0) + c * T2_CHUNK;
+#pragma unroll 2
+        for (int r = 0; r < rows; r++) {
+            const uint4 a = s[2 * r], b = s[2 * r + 1];
+#pragma unroll
+            for (int i = 0; i < T2_QPT; i++) {
+                const int dist = ham256(qr[i], a, b);
+                if (dist < b2[i]) {
+                    if (dist < b1[i]) { b2[i] = b1[i]; b1[i] = dist; bi[i] = rowBase + r; }
+                    else b2[i] = dist;
+                }
+            }
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int i = 0; i < T2_QPT; i++) {
+        const int qi = blockIdx.x * T2_QTILE + i * T2_NT + threadIdx.x;
+        if (qi < nq) {
+            orbfe_match m;
+            m.best1 = b1[i]; m.best2 = b2[i]; m.idx = bi[i]; m.accepted = 0;
+            parts[(size_t)slice * nq + qi] = m;
+        }
+    }
+}
+
+/* mode 0: best1 <= th && (float)best1 < ratio*(float)best2   (KF-Frame, src/ORBmatcher.cc:373-375)
+ * mode 1: best1 <  th && ...                                    (KF-KF,    src/ORBmatcher.cc:906-908)
+ * mode 2: knn-2 + Lowe in double: (double)(float)d0 < (double)(float)d1 * ratio, needs two rows (src/Frame.cc:1144) */
+__global__ void k_top2_merge(const orbfe_match* __restrict__ parts, int nshards, int nq, int th, float ratio, double dratio,
+                             int mode, int haveTwo, int initDist, orbfe_match* __restrict__ out) {
+    const int qi = blockIdx.x * blockDim.x + threadIdx.x;
+    if (qi >= nq) return;
+    int b1 = initDist, b2 = initDist, bi = -1;
+    for (int s = 0; s < nshards; s++) {
+        const orbfe_match m = parts[(size_t)s * nq + qi];
+        if (m.best1 < b1) { b2 = b1; b1 = m.best1; bi = m.idx; }
+        else if (m.best1 < b2) b2 = m.best1;
+        if (m.best2 < b2) b2 = m.best2; /* m.best2 >= m.best1 >= b1 here */
+    }
+    int ok;
+    if (mode == 2) ok = haveTwo && ((double)(float)b1 < (double)(float)b2 * dratio);
+    else ok = (mode == 1 ? (b1 < th) : (b1 <= th)) && ((float)b1 < __fmul_rn(ratio, (float)b2));
+    orbfe_match r;
+    r.best1 = b1; r.best2 = b2; r.idx = bi; r.accepted = ok;
+    out[qi] = r;
+}
+
+__global__ void k_pair_distances(const uint4* __restrict__ a, const uint4* __restrict__ b, long long n, int* __restrict__ out) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint4 a0 = a[2 * i], a1 = a[2 * i + 1], b0 = b[2 * i], b1 = b[2 * i + 1];
+    out[i] = __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) +
+             __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
+}
+
+struct orbfe_matcher {
+    int device;
+    int maxQ;
+    long long maxDb;
+    uint8_t* dDbOwned;     /* storage for orbfe_matcher_set_db */
+    const uint8_t* dDb;    /* current database (owned or caller's) */
+    long long ndb, indexBase;
+    uint8_t* dQ;
+    orbfe_match* dParts;   /* [maxSlices][maxQ] scratch of the partial kernel */
+    orbfe_match* dOut;
+    int maxSlices;
+    cudaStream_t stream;
+};
+
+static int top2_plan(long long ndb, int nq, int maxSlices, int* rowsPerSlice) {
+    /* enough CTAs to fill 148 SMs several times over, but slices of at least one smem stage */
+    const int qTiles = (nq + T2_QTILE - 1) / T2_QTILE;
+    int slices = std::max(1, std::min(maxSlices, (148 * 4 + qTiles - 1) / qTiles));
+    long long rps = (ndb + slices - 1) / slices;
+    rps = std::max<long long>(rps, T2_CHUNK);
+    rps = (rps + 7) / 8 * 8;
+    slices = (int)std::max<long long>(1, (ndb + rps - 1) / rps);
+    *rowsPerSlice = (int)rps;
+    return slices;
+}
+
+static int launch_top2(const uint8_t* dQ, int nq, const uint8_t* dDb, long long ndb, long long indexBase, orbfe_match* dParts,
+                       int maxSlices, int th, float ratio, double dratio, int mode, orbfe_match* dOut, cudaStream_t st) {
+    const int initDist = mode == 2 ? 257 : 256;
+    int rps = 0;
+    const int slices = top2_plan(ndb, nq, maxSlices, &rps);
+    const int qTiles = (nq + T2_QTILE - 1) / T2_QTILE;
+    k_top2_partial<<<dim3(qTiles, slices), T2_NT, 0, st>>>((const uint4*)dQ, nq, (const uint4*)dDb, ndb, indexBase, rps, initDist, dParts);
+    k_top2_merge<<<(nq + 127) / 128, 128, 0, st>>>(dParts, slices, nq, th, ratio, dratio, mode, ndb >= 2, initDist, dOut);
+    ORBFE_CUDA(cudaGetLastError());
+    return 0;
+}
+
+/* --------------------------------------------------------------------------------------------------- stereo */
+#define ST_NT 256
+static __device__ __forceinline__ int ham_rows(const uint4* a, const uint4* b) {
+    const uint4 a0 = a[0], a1 = a[1], b0 = b[0], b1 = b[1];
+    return __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) +
+           __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
+}
+
+/* One warp = one left keypoint.  Lanes stride over the right keypoints in index order (the reference's row
+ * table lists them in index order too, src/Frame.cc:814-824), keep (distance, index) minima, then the warp
+ * does the 11-shift SAD and the parabola fit.  Float steps use round-to-nearest intrinsics (no contraction). */
+__global__ void __launch_bounds__(ST_NT) k_stereo_match(const __grid_constant__ ExDesc d, ExBuffers L, ExBuffers R, float mbf,
+                                                        float minD, float maxD) {
+    const size_t f = blockIdx.y;
+    const int lane = threadIdx.x & 31;
+    const int iL = blockIdx.x * (ST_NT / 32) + (threadIdx.x >> 5);
+    const int n = L.count[f], nR = R.count[f];
+    if (iL >= n) return;
+    const size_t o = f * d.kpCap + iL;
+    float outU = -1.f, outD = -1.f;
+    int outS = -1;
+    const orbfe_keypoint kpL = L.kps[o];
+    const int levelL = kpL.octave;
+    const float vL = kpL.y, uL = kpL.x;
+    const int row = (int)vL;
+    const float minU = __fsub_rn(uL, maxD), maxU = __fsub_rn(uL, minD);
+    int best = 100, bestR = 0x7FFFFFFF; /* TH_HIGH, src/ORBmatcher.cc:36 */
+    if (!(maxU < 0)) {
+        const uint4* dL = reinterpret_cast<const uint4*>(L.desc + o * 32);
+        const orbfe_keypoint* kR = R.kps + f * d.kpCap;
+        for (int iR = lane; iR < nR; iR += 32) {
+            const orbfe_keypoint k = kR[iR];
+            const float r = __fmul_rn(2.0f, d.lv[k.octave].scale);
+            const int maxr = (int)ceilf(__fadd_rn(k.y, r)), minr = (int)floorf(__fsub_rn(k.y, r));
+            if (row < minr || row > maxr) continue;
+            if (k.octave < levelL - 1 || k.octave > levelL + 1) continue;
+            if (k.x >= minU && k.x <= maxU) {
+                const int dist = ham_rows(dL, reinterpret_cast<const uint4*>(R.desc + (f * d.kpCap + iR) * 32));
+                if (dist < best) { best = dist; bestR = iR; }
+            }
+        }
+#pragma unroll
+        for (int s = 16; s > 0; s >>= 1) {
+            const int ob = __shfl_xor_sync(0xFFFFFFFFu, best, s), oi = __shfl_xor_sync(0xFFFFFFFFu, bestR, s);
+            if (ob < best || (ob == best && oi < bestR)) { best = ob; bestR = oi; }
+        }
+    }
+    if (best < 75 && !(maxU < 0)) { /* thOrbDist = (TH_HIGH+TH_LOW)/2, src/Frame.cc:802 */
+        const LevelDesc& lv = d.lv[levelL];
+        const float uR0 = R.kps[f * d.kpCap + bestR].x;
+        const float sf = __fdiv_rn(1.0f, lv.scale); /* mvInvScaleFactors[octave] */
+        const float suL = roundf(__fmul_rn(kpL.x, sf)), svL = roundf(__fmul_rn(kpL.y, sf)), suR0 = roundf(__fmul_rn(uR0, sf));
+        const float iniu = __fsub_rn(__fadd_rn(suR0, 5.f), 5.f), endu = __fadd_rn(__fadd_rn(__fadd_rn(suR0, 5.f), 5.f), 1.f);
+        if (!(iniu < 0 || endu >= (float)lv.w)) {
+            const int y0 = (int)__fsub_rn(svL, 5.f), xl0 = (int)__fsub_rn(suL, 5.f), xr0 = (int)suR0 - 5;
+            const uint8_t* pl = L.pyr + f * d.pyrSlab + lv.pyrOff + (size_t)(y0 + ORBFE_EDGE) * lv.pitch + ORBFE_ROW_LEAD + xl0;
+            const uint8_t* pr = R.pyr + f * d.pyrSlab + lv.pyrOff + (size_t)(y0 + ORBFE_EDGE) * lv.pitch + ORBFE_ROW_LEAD + xr0;
+            int sad[11];
+#pragma unroll
+            for (int k = 0; k < 11; k++) sad[k] = 0;
+            for (int p = lane; p < 121; p += 32) {
+                const int dy = p / 11, dx = p - dy * 11;
+                const int a = pl[dy * lv.pitch + dx];
+                const uint8_t* rr = pr + dy * lv.pitch + dx - 5;
+#pragma unroll
+                for (int k = 0; k < 11; k++) sad[k] += abs(a - (int)rr[k]);
+            }
+#pragma unroll
+            for (int k = 0; k < 11; k++)
+#pragma unroll
+                for (int s = 16; s > 0; s >>= 1) sad[k] += __shfl_xor_sync(0xFFFFFFFFu, sad[k], s);
+            int bestS = 0x7FFFFFFF, bestInc = 0;
+#pragma unroll
+            for (int k = 0; k < 11; k++)
+                if (sad[k] < bestS) { bestS = sad[k]; bestInc = k - 5; }
+            if (bestInc != -5 && bestInc != 5) {
+                float d1 = 0.f, d2 = 0.f, d3 = 0.f;
+#pragma unroll
+                for (int k = 1; k < 10; k++)
+                    if (k == bestInc + 5) { d1 = (float)sad[k - 1]; d2 = (float)sad[k]; d3 = (float)sad[k + 1]; }
+                const float deltaR = __fdiv_rn(__fsub_rn(d1, d3), __fmul_rn(2.0f, __fsub_rn(__fadd_rn(d1, d3), __fmul_rn(2.0f, d2))));
+                if (!(deltaR < -1 || deltaR > 1)) {
+                    float bestuR = __fmul_rn(lv.scale, __fadd_rn(__fadd_rn(suR0, (float)bestInc), deltaR));
+                    float disparity = __fsub_rn(uL, bestuR);
+                    if (disparity >= minD && disparity < maxD) {
+                        if (disparity <= 0) {
+                            disparity = 0.01f;
+                            bestuR = (float)((double)uL - 0.01);
+                        }
+                        outD = __fdiv_rn(mbf, disparity);
+                        outU = bestuR;
+                        outS = bestS;
+                    }
+                }
+            }
+        }
+    }
+    if (lane == 0) {
+        L.uRight[o] = outU;
+        L.depth[o] = outD;
+        L.sadBest[o] = outS;
+    }
+}
+
+/* One CTA = one frame: median of the accepted SAD scores (element size/2 of the sorted list, src/Frame.cc:953-955)
+ * by a two-level histogram, then drop matches with SAD >= 1.5*1.4*median (src/Frame.cc:957-966). */
+__global__ void __launch_bounds__(256) k_stereo_median(const __grid_constant__ ExDesc d, ExBuffers L) {
+    __shared__ int s_hist[256];
+    __shared__ int s_sel, s_below, s_m;
+    const size_t f = blockIdx.x;
+    const int n = L.count[f];
+    const int* sad = L.sadBest + f * d.kpCap;
+    const int tid = threadIdx.x;
+    s_hist[tid] = 0;
+    if (tid == 0) s_m = 0;
+    __syncthreads();
+    int mine = 0;
+    for (int i = tid; i < n; i += 256) {
+        const int v = sad[i];
+        if (v >= 0) { mine++; atomicAdd(&s_hist[min(v >> 8, 255)], 1); }
+    }
+    if (mine) atomicAdd(&s_m, mine);
+    __syncthreads();
+    const int m = s_m;
+    if (m == 0) return; /* defined deviation: the reference indexes an empty vector here */
+    const int target = m / 2;
+    if (tid == 0) {
+        int run = 0, b = 0;
+        for (; b < 256; b++) { if (run + s_hist[b] > target) break; run += s_hist[b]; }
+        s_sel = b; s_below = run;
+    }
+    __syncthreads();
+    const int hi = s_sel, below = s_below;
+    __syncthreads();
+    s_hist[tid] = 0;
+    __syncthreads();
+    for (int i = tid; i < n; i += 256) {
+        const int v = sad[i];
+        if (v >= 0 && min(v >> 8, 255) == hi) atomicAdd(&s_hist[v & 255], 1);
+    }
+    __syncthreads();
+    if (tid == 0) {
+        int run = below, b = 0;
+        for (; b < 256; b++) { if (run + s_hist[b] > target) break; run += s_hist[b]; }
+        s_sel = (hi << 8) | b;
+    }
+    __syncthreads();
+    const float median = (float)s_sel;
+    const float thDist = __fmul_rn(__fmul_rn(1.5f, 1.4f), median);
+    for (int i = tid; i < n; i += 256) {
+        const int v = sad[i];
+        if (v >= 0 && !((float)v < thDist)) {
+            L.uRight[f * d.kpCap + i] = -1.f;
+            L.depth[f * d.kpCap + i] = -1.f;
+        }
+    }
+}
+
+static bool same_geometry(const orbfe_extractor* a, const orbfe_extractor* b) {
+    return a->device == b->device && a->d.nlevels == b->d.nlevels && a->d.W == b->d.W && a->d.H == b->d.H &&
+           a->d.kpCap == b->d.kpCap && a->d.pyrSlab == b->d.pyrSlab && a->params.scale_factor == b->params.scale_factor;
+}
+
+extern "C" {
+
+int orbfe_stereo_match_batch_device(orbfe_extractor* exL, orbfe_extractor* exR, int nframes, float mbf, float minD, float maxD, void* stream) {
+    if (!exL || !exR) { orbfe_set_error("null extractor"); return ORBFE_E_INVALID; }
+    if (!same_geometry(exL, exR)) { orbfe_set_error("left/right extractors differ in geometry or device"); return ORBFE_E_INVALID; }
+    if (nframes < 1 || nframes > exL->lastBatch || nframes > exR->lastBatch) { orbfe_set_error("nframes exceeds the last extracted batch"); return ORBFE_E_INVALID; }
+    ORBFE_CUDA(cudaSetDevice(exL->device));
+    cudaStream_t st = stream ? (cudaStream_t)stream : exL->stream;
+    if (!stream) ORBFE_CUDA(cudaStreamSynchronize(exR->stream)); /* right extraction ran on its own stream */
+    const bool prof = exL->profiling != 0;
+    if (prof && exL->stereoPending) { int rc = orbfe_collect_stage_times(exL); if (rc) return rc; }
+    cudaEvent_t* ev = exL->ev + ORBFE_NUM_STAGES + 1; /* two private events: the extractor's own stay untouched */
+    if (prof) ORBFE_CUDA(cudaEventRecord(ev[0], st));
+    k_stereo_match<<<dim3((exL->d.kpCap + ST_NT / 32 - 1) / (ST_NT / 32), nframes), ST_NT, 0, st>>>(exL->d, exL->b, exR->b, mbf, minD, maxD);
+    k_stereo_median<<<nframes, 256, 0, st>>>(exL->d, exL->b);
+    exL->launches += 2;
+    ORBFE_CUDA(cudaGetLastError());
+    if (prof) {
+        /* stereo is short: time both kernels as one span, reported under "stereo match" */
+        ORBFE_CUDA(cudaEventRecord(ev[1], st));
+        exL->stereoPending = 1;
+    }
+    return ORBFE_OK;
+}
+
+int orbfe_stereo_result(orbfe_extractor* exL, int frame, float* u_right, float* depth, int cap, int* n) {
+    if (!exL || frame < 0 || frame >= exL->lastBatch) { orbfe_set_error("bad frame index"); return ORBFE_E_INVALID; }
+    ORBFE_CUDA(cudaSetDevice(exL->device));
+    ORBFE_CUDA(cudaDeviceSynchronize());
+    int cnt = 0;
+    ORBFE_CUDA(cudaMemcpy(&cnt, exL->b.count + frame, sizeof(int), cudaMemcpyDeviceToHost));
+    if (n) *n = cnt;
+    if (cnt > cap) { orbfe_set_error("caller capacity %d < %d", cap, cnt); return ORBFE_E_CAPACITY; }
+    if (u_right && cnt) ORBFE_CUDA(cudaMemcpy(u_right, exL->b.uRight + (size_t)frame * exL->d.kpCap, cnt * sizeof(float), cudaMemcpyDeviceToHost));
+    if (depth && cnt) ORBFE_CUDA(cudaMemcpy(depth, exL->b.depth + (size_t)frame * exL->d.kpCap, cnt * sizeof(float), cudaMemcpyDeviceToHost));
+    return ORBFE_OK;
+}
+
+int orbfe_stereo_result_batch(orbfe_extractor* exL, int nframes, float* u_right, float* depth, int cap) {
+    if (!exL || nframes < 1 || nframes > exL->lastBatch) { orbfe_set_error("bad frame count"); return ORBFE_E_INVALID; }
+    if (cap < exL->d.kpCap) { orbfe_set_error("cap %d < keypoint capacity %d", cap, exL->d.kpCap); return ORBFE_E_CAPACITY; }
+    ORBFE_CUDA(cudaSetDevice(exL->device));
+    ORBFE_CUDA(cudaDeviceSynchronize());
+    const size_t w = (size_t)exL->d.kpCap * sizeof(float);
+    if (u_right) ORBFE_CUDA(cudaMemcpy2D(u_right, (size_t)cap * sizeof(float), exL->b.uRight, w, w, nframes, cudaMemcpyDeviceToHost));
+    if (depth) ORBFE_CUDA(cudaMemcpy2D(depth, (size_t)cap * sizeof(float), exL->b.depth, w, w, nframes, cudaMemcpyDeviceToHost));
+    return ORBFE_OK;
+}
+
+int orbfe_stereo_device_views(orbfe_extractor* exL, const float** u, const float** dd) {
+    if (!exL) return ORBFE_E_INVALID;
+    if (u) *u = exL->b.uRight;
+    if (dd) *dd = exL->b.depth;
+    return ORBFE_OK;
+}
+
+/* ------------------------------------------------------------------------------------------------- matcher */
+void orbfe_matcher_destroy(orbfe_matcher* m) {
+    if (!m) return;
+    cudaSetDevice(m->device);
+    if (m->stream) cudaStreamSynchronize(m->stream);
+    cudaFree(m->dDbOwned);
+    cudaFree(m->dQ);
+    cudaFree(m->dParts);
+    cudaFree(m->dOut);
+    if (m->stream) cudaStreamDestroy(m->stream);
+    delete m;
+}
+
+int orbfe_matcher_create(int device, int max_queries, int64_t max_db_rows, orbfe_matcher** out) {
+    if (!out || max_queries < 1 || max_db_rows < 0) { orbfe_set_error("bad argument"); return ORBFE_E_INVALID; }
+    *out = nullptr;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev) {
+        orbfe_set_error("no usable CUDA device %d (found %d); this library has no CPU path", device, ndev);
+        return ORBFE_E_CUDA;
+    }
+    ORBFE_CUDA(cudaSetDevice(device));
+    orbfe_matcher* m = new (std::nothrow) orbfe_matcher();
+    if (!m) return ORBFE_E_INVALID;
+    memset(m, 0, sizeof *m);
+    m->device = device; m->maxQ = max_queries; m->maxDb = max_db_rows;
+    m->maxSlices = 148 * 4;
+    cudaError_t e = cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess && max_db_rows > 0) e = cudaMalloc((void**)&m->dDbOwned, (size_t)max_db_rows * 32);
+    if (e == cudaSuccess) e = cudaMalloc((void**)&m->dQ, (size_t)max_queries * 32);
+    if (e == cudaSuccess) e = cudaMalloc((void**)&m->dParts, (size_t)m->maxSlices * max_queries * sizeof(orbfe_match));
+    if (e == cudaSuccess) e = cudaMalloc((void**)&m->dOut, (size_t)max_queries * sizeof(orbfe_match));
+    if (e != cudaSuccess) { const int rc = orbfe_cuda_fail(e, "matcher allocation"); orbfe_matcher_destroy(m); return rc; }
+    *out = m;
+    return ORBFE_OK;
+}
+
+int orbfe_matcher_set_db(orbfe_matcher* m, const uint8_t* h_db, int64_t rows, int64_t index_base) {
+    if (!m || (rows > 0 && !h_db) || rows < 0) { orbfe_set_error("bad argument"); return ORBFE_E_INVALID; }
+    if (rows > m->maxDb) { orbfe_set_error("database of %lld rows exceeds capacity %lld", (long long)rows, m->maxDb); return ORBFE_E_CAPACITY; }
+    ORBFE_CUDA(cudaSetDevice(m->device));
+    if (rows) ORBFE_CUDA(cudaMemcpyAsync(m->dDbOwned, h_db, (size_t)rows * 32, cudaMemcpyHostToDevice, m->stream));
+    ORBFE_CUDA(cudaStreamSynchronize(m->stream));
+    m->dDb = m->dDbOwned; m->ndb = rows; m->indexBase = index_base;
+    return ORBFE_OK;
+}
+
+int orbfe_matcher_set_db_device(orbfe_matcher* m, const uint8_t* d_db, int64_t rows, int64_t index_base) {
+    if (!m || (rows > 0 && !d_db) || rows < 0) { orbfe_set_error("bad argument"); return ORBFE_E_INVALID; }
+    if (((uintptr_t)d_db & 15) != 0) { orbfe_set_error("database pointer must be 16-byte aligned"); return ORBFE_E_INVALID; }
+    m->dDb = d_db; m->ndb = rows; m->indexBase = index_base;
+    return ORBFE_OK;
+}
+
+int orbfe_matcher_top2_device(orbfe_matcher* m, const uint8_t* d_queries, int nq, int th, float ratio, int strict_lt,
+                              orbfe_match* d_out, void* stream) {
+    if (!m || !d_queries || !d_out || nq < 1) { orbfe_set_error("bad argument"); return ORBFE_E_INVALID; }
+    if (nq > m->maxQ) { orbfe_set_error("%d queries exceed capacity %d", nq, m->maxQ); return ORBFE_E_CAPACITY; }
+    if (((uintptr_t)d_queries & 15) != 0) { orbfe_set_error("query pointer must be 16-byte aligned"); return ORBFE_E_INVALID; }
+    ORBFE_CUDA(cudaSetDevice(m->device));
+    return launch_top2(d_queries, nq, m->dDb, m->ndb, m->indexBase, m->dParts, m->maxSlices, th, ratio, 0.0, strict_lt ? 1 : 0,
+                       d_out, stream ? (cudaStream_t)stream : m->stream);
+}
+
+int orbfe_matcher_top2(orbfe_matcher* m, const uint8_t* h_queries, int nq, int th, float ratio, int strict_lt, orbfe_match* h_out) {
+    if (!m || !h_queries || !h_out || nq < 1) { orbfe_set_error("bad argument"); return ORBFE_E_INVALID; }
+    if (nq > m->maxQ) { orbfe_set_error("%d queries exceed capacity %d", nq, m->maxQ); return ORBFE_E_CAPACITY; }
+    ORBFE_CUDA(cudaSetDevice(m->device));
+    ORBFE_CUDA(cudaMemcpyAsync(m->dQ, h_queries, (size_t)nq * 32, cudaMemcpyHostToDevice, m->stream));
+    int rc = launch_top2(m->dQ, nq, m->dDb, m->ndb, m->indexBase, m->dParts, m->maxSlices, th, ratio, 0.0, strict_lt ? 1 : 0, m->dOut, m->stream);
+    if (rc) return rc;
+    ORBFE_CUDA(cudaMemcpyAsync(h_out, m->dOut, (size_t)nq * sizeof(orbfe_match), cudaMemcpyDeviceToHost, m->stream));
+    ORBFE_CUDA(cudaStreamSynchronize(m->stream));
+    return ORBFE_OK;
+}
+
+int orbfe_top2_merge_device(int device, const orbfe_match* d_parts, int nshards, int nq, int th, float ratio, int strict_lt,
+                            orbfe_match* d_out, void* stream) {
+    if (!d_parts || !d_out || nshards < 1 || nq < 1) { orbfe_set_error("bad argument"); return ORBFE_E_INVALID; }
+    ORBFE_CUDA(cudaSetDevice(device));
+    k_top2_merge<<<(nq + 127) / 128, 128, 0, (cudaStream_t)stream>>>(d_parts, nshards, nq, th, ratio, 0.0, strict_lt ? 1 : 0, 1, 256, d_out);
+    ORBFE_CUDA(cudaGetLastError());
+    return ORBFE_OK;
+}
+
+int orbfe_hamming_top2(int device, const uint8_t* q, int nq, const uint8_t* db, int64_t ndb, int th, float ratio, int strict_lt, orbfe_match* out) {
+    orbfe_matcher* m = nullptr;
+    int rc = orbfe_matcher_create(device, std::max(nq, 1), std::max<int64_t>(ndb, 1), &m);
+    if (rc) return rc;
+    rc = orbfe_matcher_set_db(m, db, ndb, 0);
+    if (!rc) rc = orbfe_matcher_top2(m, q, nq, th, ratio, strict_lt, out);
+    orbfe_matcher_destroy(m);
+    return rc;
+}
+
+int orbfe_knn2_ratio(int device, const uint8_t* q, int nq, const uint8_t* t, int nt, double ratio, int32_t* match, int32_t* d0, int32_t* d1) {
+    if (!q || !match || nq < 1 || nt < 0 || (nt > 0 && !t)) { orbfe_set_error("bad argument"); return ORBFE_E_INVALID; }
+    orbfe_matcher* m = nullptr;
+    int rc = orbfe_matcher_create(device, nq, std::max(nt, 1), &m);
+    if (rc) return rc;
+    rc = orbfe_matcher_set_db(m, t, nt, 0);
+    orbfe_match* h = new (std::nothrow) orbfe_match[nq];
+    if (!rc && h) {
+        cudaSetDevice(device);
+        cudaError_t e = cudaMemcpyAsync(m->dQ, q, (size_t)nq * 32, cudaMemcpyHostToDevice, m->stream);
+        if (e == cudaSuccess) {
+            rc = launch_top2(m->dQ, nq, m->dDb, m->ndb, 0, m->dParts, m->maxSlices, 0, 0.f, ratio, 2, m->dOut, m->stream);
+            if (!rc) e = cudaMemcpyAsync(h, m->dOut, (size_t)nq * sizeof(orbfe_match), cudaMemcpyDeviceToHost, m->stream);
+            if (!rc && e == cudaSuccess) e = cudaStreamSynchronize(m->stream);
+        }
+        if (e != cudaSuccess) rc = orbfe_cuda_fail(e, "knn2");
+        if (!rc)
+            for (int i = 0; i < nq; i++) {
+                match[i] = h[i].accepted ? h[i].idx : -1;
+                if (d0) d0[i] = nt >= 1 ? h[i].best1 : -1;
+                if (d1) d1[i] = nt >= 2 ? h[i].best2 : -1;
+            }
+    }
+    delete[] h;
+    orbfe_matcher_destroy(m);
+    return rc;
+}
+
+int orbfe_descriptor_distances(int device, const uint8_t* a, const uint8_t* b, int64_t n, int32_t* out) {
+    if (!a || !b || !out || n < 1) { orbfe_set_error("bad argument"); return ORBFE_E_INVALID; }
+    ORBFE_CUDA(cudaSetDevice(device));
+    uint8_t *da = nullptr, *db = nullptr;
+    int* dout = nullptr;
+    cudaError_t e = cudaMalloc((void**)&da, (size_t)n * 32);
+    if (e == cudaSuccess) e = cudaMalloc((void**)&db, (size_t)n * 32);
+    if (e == cudaSuccess) e = cudaMalloc((void**)&dout, (size_t)n * 4);
+    if (e == cudaSuccess) e = cudaMemcpy(da, a, (size_t)n * 32, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(db, b, (size_t)n * 32, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) {
+        k_pair_distances<<<(unsigned)((n + 255) / 256), 256>>>((const uint4*)da, (const uint4*)db, n, dout);
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaMemcpy(out, dout, (size_t)n * 4, cudaMemcpyDeviceToHost);
+    cudaFree(da); cudaFree(db); cudaFree(dout);
+    if (e != cudaSuccess) return orbfe_cuda_fail(e, "descriptor_distances");
+    return ORBFE_OK;
+}
+
+}  /* extern "C" */

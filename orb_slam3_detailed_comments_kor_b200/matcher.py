@@ -1,0 +1,127 @@
+"""Host-side mirror of the descriptor-matching core of ORB_SLAM3::ORBmatcher and Frame over the C ABI.
+
+Reference surface: ORBmatcher(nnratio, checkOri), TH_LOW/TH_HIGH, static DescriptorDistance
+(/root/reference/include/ORBmatcher.h:35-111, src/ORBmatcher.cc:36-42, 2591-2607); the top-2 core of SearchByBoW
+(src/ORBmatcher.cc:311-375, 870-908); Frame::ComputeStereoMatches / ComputeStereoFishEyeMatches
+(src/Frame.cc:797-967, 1119-1159)."""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from ._lib import MATCH_DTYPE, check, ptr
+
+
+class DescriptorDatabase:
+    """A shard of map-point descriptors resident on one GPU (rows index_base .. index_base+rows)."""
+
+    def __init__(self, max_rows, max_queries=4096, device=0):
+        self._L = _lib.lib()
+        self._h = C.c_void_p()
+        check(self._L.orbfe_matcher_create(device, max_queries, max_rows, C.byref(self._h)))
+        self.device, self.max_queries = device, max_queries
+
+    def close(self):
+        if getattr(self, "_h", None) and self._h.value:
+            self._L.orbfe_matcher_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set(self, db, index_base=0):
+        db = np.ascontiguousarray(db, np.uint8)
+        check(self._L.orbfe_matcher_set_db(self._h, ptr(db), db.shape[0], index_base))
+
+    def set_device(self, d_ptr, rows, index_base=0):
+        check(self._L.orbfe_matcher_set_db_device(self._h, C.c_void_p(d_ptr), rows, index_base))
+
+    def top2(self, queries, th, ratio, strict_lt):
+        q = np.ascontiguousarray(queries, np.uint8)
+        out = np.zeros(q.shape[0], MATCH_DTYPE)
+        check(self._L.orbfe_matcher_top2(self._h, ptr(q), q.shape[0], th, ratio, int(strict_lt), ptr(out)))
+        return out
+
+    def top2_device(self, d_q, nq, th, ratio, strict_lt, d_out, stream=None):
+        check(self._L.orbfe_matcher_top2_device(self._h, C.c_void_p(d_q), nq, th, ratio, int(strict_lt), C.c_void_p(d_out),
+                                                C.c_void_p(stream) if stream else None))
+
+
+class ORBmatcher:
+    TH_HIGH = 100       # src/ORBmatcher.cc:36
+    TH_LOW = 50         # src/ORBmatcher.cc:37
+    HISTO_LENGTH = 30   # src/ORBmatcher.cc:38
+
+    def __init__(self, nnratio=0.6, checkOri=True, device=0):
+        self.mfNNratio = float(nnratio)
+        self.mbCheckOrientation = bool(checkOri)
+        self.device = device
+
+    @staticmethod
+    def DescriptorDistance(a, b, device=0):
+        """Hamming distance of 32-byte rows; a, b may be single rows or [n,32] batches (GPU, src/ORBmatcher.cc:2591)."""
+        a2 = np.ascontiguousarray(np.atleast_2d(a), np.uint8)
+        b2 = np.ascontiguousarray(np.atleast_2d(b), np.uint8)
+        out = np.zeros(a2.shape[0], np.int32)
+        check(_lib.lib().orbfe_descriptor_distances(device, ptr(a2), ptr(b2), a2.shape[0], ptr(out)))
+        return int(out[0]) if np.ndim(a) == 1 else out
+
+    def search_top2(self, queries, database, kf_kf=False):
+        """Brute-force top-2 of SearchByBoW: kf_kf=False -> `best1 <= TH_LOW` (KF-Frame), True -> `<` (KF-KF)."""
+        q = np.ascontiguousarray(queries, np.uint8)
+        db = np.ascontiguousarray(database, np.uint8)
+        out = np.zeros(q.shape[0], MATCH_DTYPE)
+        check(_lib.lib().orbfe_hamming_top2(self.device, ptr(q), q.shape[0], ptr(db), db.shape[0], self.TH_LOW,
+                                            self.mfNNratio, int(kf_kf), ptr(out)))
+        return out
+
+
+def merge_top2_device(device, d_parts, nshards, nq, th, ratio, strict_lt, d_out, stream=None):
+    check(_lib.lib().orbfe_top2_merge_device(device, C.c_void_p(d_parts), nshards, nq, th, ratio, int(strict_lt),
+                                             C.c_void_p(d_out), C.c_void_p(stream) if stream else None))
+
+
+def merge_top2_host(parts, th, ratio, strict_lt):
+    """Host statement of the shard merge (used by the gloo CPU tests of the multi-rank plumbing; same rule as
+    k_top2_merge): parts is [nshards, nq] MATCH_DTYPE in ascending shard (= global row) order."""
+    parts = np.asarray(parts)
+    ns, nq = parts.shape
+    out = np.zeros(nq, MATCH_DTYPE)
+    b1 = np.full(nq, 256, np.int32); b2 = b1.copy(); bi = np.full(nq, -1, np.int32)
+    for s in range(ns):
+        d1, d2, ix = parts[s]["best1"], parts[s]["best2"], parts[s]["idx"]
+        lt = d1 < b1
+        b2 = np.where(lt, b1, np.where(d1 < b2, d1, b2))
+        bi = np.where(lt, ix, bi)
+        b1 = np.where(lt, d1, b1)
+        b2 = np.minimum(b2, d2)
+    out["best1"], out["best2"], out["idx"] = b1, b2, bi
+    th_ok = (b1 < th) if strict_lt else (b1 <= th)
+    out["accepted"] = th_ok & (b1.astype(np.float32) < np.float32(ratio) * b2.astype(np.float32))
+    return out
+
+
+def compute_stereo_matches(exL, exR, nframes, mbf, minD, maxD, stream=None):
+    """Frame::ComputeStereoMatches on the frames exL/exR extracted last (device resident)."""
+    check(_lib.lib().orbfe_stereo_match_batch_device(exL.handle, exR.handle, nframes, mbf, minD, maxD,
+                                                     C.c_void_p(stream) if stream else None))
+
+
+def stereo_result(exL, frame):
+    u = np.zeros(exL.capacity, np.float32)
+    d = np.zeros(exL.capacity, np.float32)
+    n = C.c_int(0)
+    check(_lib.lib().orbfe_stereo_result(exL.handle, frame, ptr(u), ptr(d), exL.capacity, C.byref(n)))
+    return u[:n.value], d[:n.value]
+
+
+def knn2_ratio(queries, train, ratio=0.7, device=0):
+    """BFMatcher(NORM_HAMMING).knnMatch(k=2) + Lowe ratio of ComputeStereoFishEyeMatches (src/Frame.cc:1137-1144)."""
+    q = np.ascontiguousarray(queries, np.uint8)
+    t = np.ascontiguousarray(train, np.uint8)
+    m = np.zeros(q.shape[0], np.int32); d0 = m.copy(); d1 = m.copy()
+    check(_lib.lib().orbfe_knn2_ratio(device, ptr(q), q.shape[0], ptr(t), t.shape[0], float(ratio), ptr(m), ptr(d0), ptr(d1)))
+    return m, d0, d1

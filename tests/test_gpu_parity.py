@@ -1,0 +1,272 @@
+"""GPU parity tests (-m gpu): liborbfe.so, called through its C ABI, against the CPU oracle and the cv2 goldens.
+
+Bar: bit-exact pyramid pixels, FAST candidates (x, y, score), blurred pixels, keypoints (x, y, size, response,
+octave, order), descriptors, monoIndex, match indices/distances, stereo uRight/depth; angles within 1e-3 degrees
+(north_star), in practice identical bits."""
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+from oracle import orb_oracle as O                                        # noqa: E402
+from orb_slam3_detailed_comments_kor_b200 import ORBextractor, synth        # noqa: E402
+from orb_slam3_detailed_comments_kor_b200 import matcher as M               # noqa: E402
+from orb_slam3_detailed_comments_kor_b200._lib import KP_DTYPE, OrbfeError  # noqa: E402
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+ANGLE_TOL_DEG = 1e-3
+
+SHAPES = {
+    # name: (W, H, seed, (nfeatures, scale, levels, iniTh, minTh), lappings)
+    "euroc": (752, 480, 0, (1200, 1.2, 8, 20, 7), [(0, 0), (200, 400)]),
+    "tumvi": (512, 512, 1, (1500, 1.2, 8, 20, 7), [(0, 511)]),
+    "kitti": (1241, 376, 2, (2000, 1.2, 8, 20, 7), [(0, 0), (0, 1000)]),
+    "small": (160, 120, 3, (300, 1.2, 4, 20, 7), [(0, 0)]),
+    "init5x": (752, 480, 11, (6000, 1.2, 8, 20, 7), [(0, 1000)]),     # mpIniORBextractor, src/Tracking.cc:1157
+}
+
+
+def kmat(k):
+    return np.stack([k["x"], k["y"], k["size"], k["angle"], k["response"], k["octave"].astype(np.float32)], 1)
+
+
+def assert_same_keypoints(got, want, what=""):
+    assert len(got) == len(want), "%s: %d vs %d keypoints" % (what, len(got), len(want))
+    g, w = kmat(got), kmat(want)
+    cols = [0, 1, 2, 4, 5]
+    bad = np.nonzero((g[:, cols] != w[:, cols]).any(1))[0]
+    assert len(bad) == 0, "%s: first differing keypoint %d: %s vs %s" % (what, bad[0], g[bad[0]], w[bad[0]])
+    assert np.max(np.abs(g[:, 3] - w[:, 3]), initial=0) <= ANGLE_TOL_DEG, what
+    assert np.all(got["class_id"] == -1)
+
+
+def compare_stages(ex, orc, nlevels, frame=0):
+    for l in range(nlevels):
+        assert ex.level_size(l) == orc.level_size(l)
+        assert np.array_equal(ex.pyramid_level(l, frame, padded=True), orc.pyramid_level(l, padded=True)), "pyramid level %d" % l
+        gc, oc = ex.fast_candidates(l, frame), orc.fast_candidates(l)
+        assert len(gc) == len(oc), "FAST count level %d: %d vs %d" % (l, len(gc), len(oc))
+        for fld in ("x", "y", "response"):
+            assert np.array_equal(gc[fld], oc[fld]), "FAST %s level %d" % (fld, l)
+        ob = orc.blurred_level(l)
+        if ob is not None:
+            assert np.array_equal(ex.blurred_level(l, frame), ob), "blur level %d" % l
+
+
+@pytest.mark.parametrize("name", list(SHAPES))
+def test_extractor_matches_oracle(name):
+    W, H, seed, params, laps = SHAPES[name]
+    img = synth.frame(seed, W, H)
+    ex = ORBextractor(*params, width=W, height=H)
+    orc = O.OracleExtractor(*params)
+    assert list(ex.features_per_level()) == orc.quotas()
+    assert list(ex.umax()) == orc.umax()
+    assert np.array_equal(ex.GetScaleFactors(), np.array(orc.scale_factors(), np.float32))
+    for lap in laps:
+        mono, kps, desc = ex(img, lap)
+        omono, okps, odesc = orc(img, lap)
+        assert mono == omono
+        assert_same_keypoints(kps, okps, "%s lap %s" % (name, lap))
+        assert np.array_equal(desc, odesc)
+    compare_stages(ex, orc, params[2])
+    ex.close()
+
+
+@pytest.mark.parametrize("name", ["euroc", "tumvi", "kitti", "small", "noise", "lowc"])
+def test_extractor_matches_cv2_goldens(name):
+    g = np.load(os.path.join(GOLD, name + ".npz"))
+    W, H = [int(v) for v in g["wh"]]
+    img = g["imgL"] if "imgL" in g else synth.stereo_pair(int(g["seed"][0]), W, H)[0]
+    p = g["params"]
+    ex = ORBextractor(int(p[0]), float(p[1]), int(p[2]), int(p[3]), int(p[4]), width=W, height=H)
+    li = 0
+    while "lap%d" % li in g:
+        lap = tuple(int(v) for v in g["lap%d" % li])
+        mono, kps, desc = ex(img, lap)
+        assert mono == int(g["mono%d" % li][0])
+        want = g["kps%d" % li]
+        got = kmat(kps)
+        assert got.shape == want.shape
+        assert np.array_equal(got[:, [0, 1, 2, 4, 5]], want[:, [0, 1, 2, 4, 5]])
+        assert np.max(np.abs(got[:, 3] - want[:, 3]), initial=0) <= ANGLE_TOL_DEG
+        assert np.array_equal(desc, g["desc%d" % li])
+        li += 1
+    for l in range(int(p[2])):
+        c = ex.fast_candidates(l)
+        got = np.stack([c["x"], c["y"], c["response"]], 1).astype(np.int32).reshape(-1, 3)
+        assert np.array_equal(got, g["cand%d" % l]), "FAST candidates level %d" % l
+    ex.close()
+
+
+def test_batch_paths_agree_with_oracle():
+    import torch
+    W, H, params, nb = 752, 480, (1200, 1.2, 8, 20, 7), 6
+    imgs = np.stack([synth.frame(100 + i, W, H) for i in range(nb)])
+    imgs[3] = 128                                        # a featureless frame inside the batch -> 0 keypoints
+    ex = ORBextractor(*params, width=W, height=H, max_batch=nb)
+    cnt, mono, kps, desc = ex.extract_batch_host(imgs, (0, 0))
+    d_imgs = torch.from_numpy(imgs).cuda()
+    ex.extract_batch_device(d_imgs.data_ptr(), nb, (0, 0), torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    cnt2, mono2 = ex.batch_counts(nb)
+    assert np.array_equal(cnt, cnt2) and np.array_equal(mono, mono2)
+    orc = O.OracleExtractor(*params)
+    for f in range(nb):
+        omono, okps, odesc = orc(imgs[f], (0, 0))
+        assert cnt[f] == len(okps) and mono[f] == omono
+        assert_same_keypoints(kps[f, :cnt[f]], okps, "frame %d" % f)
+        assert np.array_equal(desc[f, :cnt[f]], odesc)
+        m2, k2, d2 = ex.batch_result(f)
+        assert m2 == omono and np.array_equal(d2, odesc)
+        assert_same_keypoints(k2, okps, "device frame %d" % f)
+        if f in (0, nb - 1):
+            compare_stages(ex, orc, params[2], frame=f)
+    assert cnt[3] == 0
+    ex.close()
+
+
+def test_error_behaviour():
+    ex = ORBextractor(1200, 1.2, 8, 20, 7, width=752, height=480)
+    mono, kps, desc = ex(np.zeros((0, 0), np.uint8))
+    assert mono == -1 and len(kps) == 0                 # src/ORBextractor.cc:1072-1073
+    with pytest.raises(OrbfeError):
+        ex(np.zeros((100, 100), np.uint8))               # shape fixed at creation
+    with pytest.raises(OrbfeError):
+        ORBextractor(1200, 1.2, 8, 20, 7, width=100, height=80)   # level 7 too small for the 35 px grid
+    ex.close()
+
+
+@pytest.mark.parametrize("name,stereo", [("euroc", (47.90639, 435.2047)), ("kitti", (386.1448, 718.856))])
+def test_stereo_matches_oracle_and_golden(name, stereo):
+    W, H, seed, params, _ = SHAPES[name]
+    L, R = synth.stereo_pair(seed, W, H)
+    exL = ORBextractor(*params, width=W, height=H)
+    exR = ORBextractor(*params, width=W, height=H)
+    monoL, kL, dL = exL(L, (0, 0))
+    monoR, kR, dR = exR(R, (0, 0))
+    M.compute_stereo_matches(exL, exR, 1, stereo[0], 0.0, stereo[1])
+    u, d = M.stereo_result(exL, 0)
+    oL, oR = O.OracleExtractor(*params), O.OracleExtractor(*params)
+    _, okL, odL = oL(L, (0, 0))
+    _, okR, odR = oR(R, (0, 0))
+    kept, ou, od = O.stereo_match(oL, oR, okL, odL, okR, odR, stereo[0], 0.0, stereo[1])
+    assert kept > 50
+    assert np.array_equal(u, ou), "uRight: %d differ" % int((u != ou).sum())
+    assert np.array_equal(d, od)
+    g = np.load(os.path.join(GOLD, name + ".npz"))
+    assert np.array_equal(u, g["uRight"]) and np.array_equal(d, g["depth"])
+    exL.close(); exR.close()
+
+
+def test_stereo_batch_and_no_match_frame():
+    W, H, params, nb = 752, 480, (1200, 1.2, 8, 20, 7), 3
+    pairs = [synth.stereo_pair(200 + i, W, H) for i in range(nb)]
+    Ls = np.stack([p[0] for p in pairs]); Rs = np.stack([p[1] for p in pairs])
+    Rs[1] = 128                                          # right image without features: no matches, no median cut
+    exL = ORBextractor(*params, width=W, height=H, max_batch=nb)
+    exR = ORBextractor(*params, width=W, height=H, max_batch=nb)
+    cntL, _, kL, dL = exL.extract_batch_host(Ls)
+    cntR, _, kR, dR = exR.extract_batch_host(Rs)
+    M.compute_stereo_matches(exL, exR, nb, 47.90639, 0.0, 435.2047)
+    for f in range(nb):
+        u, d = M.stereo_result(exL, f)
+        oL, oR = O.OracleExtractor(*params), O.OracleExtractor(*params)
+        _, okL, odL = oL(Ls[f]); _, okR, odR = oR(Rs[f])
+        kept, ou, od = O.stereo_match(oL, oR, okL, odL, okR, odR, 47.90639, 0.0, 435.2047)
+        assert np.array_equal(u, ou) and np.array_equal(d, od), "frame %d" % f
+        if f == 1:
+            assert kept == 0 and np.all(u == -1)
+    exL.close(); exR.close()
+
+
+def test_descriptor_distance_known_answers():
+    z = np.zeros(32, np.uint8); o = np.full(32, 255, np.uint8)
+    one = z.copy(); one[9] = 0x40
+    assert M.ORBmatcher.DescriptorDistance(z, z) == 0
+    assert M.ORBmatcher.DescriptorDistance(z, o) == 256
+    assert M.ORBmatcher.DescriptorDistance(z, one) == 1
+    rng = np.random.RandomState(0)
+    a = rng.randint(0, 256, (1000, 32)).astype(np.uint8); b = rng.randint(0, 256, (1000, 32)).astype(np.uint8)
+    want = np.unpackbits(a ^ b, axis=1).sum(1)
+    assert np.array_equal(M.ORBmatcher.DescriptorDistance(a, b), want)
+
+
+@pytest.mark.parametrize("nq,ndb", [(1, 1), (3, 2), (37, 300), (1024, 5000), (1500, 70001), (4096, 20000)])
+@pytest.mark.parametrize("strict", [False, True])
+def test_top2_matches_oracle(nq, ndb, strict):
+    db, q = synth.descriptors(nq * 7 + ndb, max(ndb, 2), nq)
+    db = db[:ndb].copy()
+    if ndb > 100:
+        db[ndb // 2] = db[3]                             # planted duplicate rows: ties -> lowest index
+        q[0] = db[3]
+    m = M.ORBmatcher(0.9, True)
+    got = m.search_top2(q, db, kf_kf=strict)
+    want = O.hamming_top2(q, db, 50, 0.9, strict)
+    for fld in ("best1", "best2", "idx", "accepted"):
+        assert np.array_equal(got[fld], want[fld]), fld
+    if ndb > 100:
+        assert got["idx"][0] == 3 and got["best1"][0] == 0 and got["best2"][0] == 0
+
+
+def test_top2_full_size_properties_and_sharding():
+    """Config 5 size (4096 x 2^20): a sample of queries against the oracle, planted matches recovered, and the
+    8-shard + merge path identical to the single-database path (emulates the NCCL merge on one GPU)."""
+    import torch
+    nq, ndb, shards = 4096, 1 << 20, 8
+    db, q = synth.descriptors(5, ndb, nq)
+    whole = M.DescriptorDatabase(ndb, nq)
+    whole.set(db)
+    full = whole.top2(q, 50, 0.9, False)
+    sample = np.arange(0, nq, 128)
+    want = O.hamming_top2(q[sample], db, 50, 0.9, False)
+    for fld in ("best1", "best2", "idx", "accepted"):
+        assert np.array_equal(full[fld][sample], want[fld]), fld
+    planted = full[0::4]
+    assert np.all(planted["best1"] <= 60) and planted["accepted"].sum() > 500
+    assert np.all(full["best2"] >= full["best1"]) and np.all(full["idx"] >= 0)
+    # sharded: per-shard top-2 on contiguous row ranges, then the merge kernel
+    rows = ndb // shards
+    d_q = torch.from_numpy(q).cuda()
+    d_parts = torch.zeros((shards, nq, 4), dtype=torch.int32, device="cuda")
+    st = torch.cuda.current_stream().cuda_stream
+    dbs = []
+    for s in range(shards):
+        sd = M.DescriptorDatabase(rows, nq)
+        sd.set(db[s * rows:(s + 1) * rows], index_base=s * rows)
+        sd.top2_device(d_q.data_ptr(), nq, 50, 0.9, False, d_parts[s].data_ptr(), st)
+        dbs.append(sd)
+    d_out = torch.zeros((nq, 4), dtype=torch.int32, device="cuda")
+    M.merge_top2_device(0, d_parts.data_ptr(), shards, nq, 50, 0.9, False, d_out.data_ptr(), st)
+    torch.cuda.synchronize()
+    merged = d_out.cpu().numpy()
+    assert np.array_equal(merged[:, 0], full["best1"]) and np.array_equal(merged[:, 1], full["best2"])
+    assert np.array_equal(merged[:, 2], full["idx"]) and np.array_equal(merged[:, 3], full["accepted"])
+    host = M.merge_top2_host(d_parts.cpu().numpy().view(M.MATCH_DTYPE).reshape(shards, nq), 50, 0.9, False)
+    assert np.array_equal(host["idx"], full["idx"]) and np.array_equal(host["accepted"], full["accepted"])
+
+
+@pytest.mark.parametrize("name", ["tumvi", "noise"])
+def test_knn2_matches_oracle_and_golden(name):
+    g = np.load(os.path.join(GOLD, name + ".npz"))
+    W, H = [int(v) for v in g["wh"]]
+    L, R = (g["imgL"], g["imgR"]) if "imgL" in g else synth.stereo_pair(int(g["seed"][0]), W, H)
+    p = g["params"]
+    params = (int(p[0]), float(p[1]), int(p[2]), int(p[3]), int(p[4]))
+    li = max(i for i in range(4) if "lap%d" % i in g)
+    lap = tuple(int(v) for v in g["lap%d" % li])
+    exL = ORBextractor(*params, width=W, height=H); exR = ORBextractor(*params, width=W, height=H)
+    monoL, kL, dL = exL(L, lap); monoR, kR, dR = exR(R, lap)
+    m, d0, d1 = M.knn2_ratio(dL[monoL:], dR[monoR:], 0.7)
+    om, od0, od1 = O.knn2_ratio(dL[monoL:], dR[monoR:], 0.7)
+    assert np.array_equal(m, om) and np.array_equal(d0, od0) and np.array_equal(d1, od1)
+    assert np.array_equal(m, g["knn_match"]) and np.array_equal(np.stack([d0, d1], 1), g["knn_d01"])
+    exL.close(); exR.close()
+
+
+def test_knn2_degenerate_train_sizes():
+    q = np.random.RandomState(1).randint(0, 256, (5, 32)).astype(np.uint8)
+    m, d0, d1 = M.knn2_ratio(q, q[:1], 0.7)            # one train row: knnMatch returns <2 -> rejected (Frame.cc:1144)
+    om, od0, od1 = O.knn2_ratio(q, q[:1], 0.7)
+    assert np.array_equal(m, om) and np.all(m == -1) and np.array_equal(d0, od0) and np.array_equal(d1, od1)
