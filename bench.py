@@ -222,7 +222,12 @@ def main():
     dL, dR = hL.cuda(non_blocking=True), hR.cuda(non_blocking=True)
     exL = ORBextractor(*PARAMS, width=W, height=H, device=local_rank, max_batch=P)
     exR = ORBextractor(*PARAMS, width=W, height=H, device=local_rank, max_batch=P)
-    st = torch.cuda.current_stream().cuda_stream
+    # a real (non-default) stream: every kernel of the step is enqueued on it and the CUDA events below are recorded
+    # on it, so the events see exactly the timed work (a NULL stream would make the library use its own streams)
+    tstream = torch.cuda.Stream()
+    torch.cuda.set_stream(tstream)
+    st = tstream.cuda_stream
+    assert st != 0
     L = _lib.lib()
 
     def step():

@@ -141,7 +141,7 @@ __global__ void __launch_bounds__(256) k_blur7(const __grid_constant__ ExDesc d,
      (k) == 9 ? -3 * TP - 1 : (k) == 10 ? -2 * TP - 2 : (k) == 11 ? -TP - 3 : (k) == 12 ? -3 :              \
      (k) == 13 ? TP - 3 : (k) == 14 ? 2 * TP - 2 : 3 * TP - 1)
 
-static __device__ __forceinline__ bool run9(uint32_t m) {
+static __host__ __device__ __forceinline__ bool run9(uint32_t m) {
     m |= m << 16;
     uint32_t x = m & (m >> 1);
     x &= x >> 2;
@@ -151,7 +151,7 @@ static __device__ __forceinline__ bool run9(uint32_t m) {
 }
 
 /* corner at threshold t  <=>  9 contiguous ring pixels all > v+t or all < v-t */
-static __device__ __forceinline__ bool fast_is_corner(const uint8_t* c, int t) {
+static __host__ __device__ __forceinline__ bool fast_is_corner(const uint8_t* c, int t) {
     const int v = c[0];
     const int hi = v + t, lo = v - t;
     const int p0 = c[RING_OFF(0, FAST_TP)], p8 = c[RING_OFF(8, FAST_TP)];
@@ -170,25 +170,31 @@ static __device__ __forceinline__ bool fast_is_corner(const uint8_t* c, int t) {
     return run9(B) || run9(D);
 }
 
-/* cv::FAST cornerScore: (max over the 16 arcs of min |difference| with a common sign) - 1 */
-static __device__ __forceinline__ int fast_score(const uint8_t* c) {
+/* cv::FAST cornerScore = m - 1 with m = max over the 16 arcs of max(min_k (v - r_k), min_k (r_k - v)).
+ * Evaluated on the raw ring values: min_k (v - r_k) = v - max_k r_k and min_k (r_k - v) = min_k r_k - v, so
+ * m = max(v - min_arcs(max_arc r), max_arcs(min_arc r) - v).  Besides being cheaper this keeps every min/max
+ * operand a plain non-negated register: nvcc 12.9 folds a negation into VIMNMX3 on sm_100a and the result
+ * loses the sign (found by tools/fast_device_test3.cu: max(m, max(lo, -hi)) returned max(m, lo, hi)). */
+static __host__ __device__ __forceinline__ int fast_score(const uint8_t* c) {
     const int v = c[0];
-    int d[16];
+    int r[16];
 #pragma unroll
-    for (int k = 0; k < 16; k++) d[k] = v - (int)c[RING_OFF(k, FAST_TP)];
+    for (int k = 0; k < 16; k++) r[k] = (int)c[RING_OFF(k, FAST_TP)];
     int lo2[16], hi2[16], lo4[16], hi4[16];
 #pragma unroll
-    for (int k = 0; k < 16; k++) { lo2[k] = min(d[k], d[(k + 1) & 15]); hi2[k] = max(d[k], d[(k + 1) & 15]); }
+    for (int k = 0; k < 16; k++) { lo2[k] = min(r[k], r[(k + 1) & 15]); hi2[k] = max(r[k], r[(k + 1) & 15]); }
 #pragma unroll
     for (int k = 0; k < 16; k++) { lo4[k] = min(lo2[k], lo2[(k + 2) & 15]); hi4[k] = max(hi2[k], hi2[(k + 2) & 15]); }
-    int m = -256;
+    int minOfMax = 255, maxOfMin = 0;
 #pragma unroll
     for (int k = 0; k < 16; k++) {
-        const int lo9 = min(min(lo4[k], lo4[(k + 4) & 15]), d[(k + 8) & 15]);
-        const int hi9 = max(max(hi4[k], hi4[(k + 4) & 15]), d[(k + 8) & 15]);
-        m = max(m, max(lo9, -hi9));
+        const int lo9 = min(min(lo4[k], lo4[(k + 4) & 15]), r[(k + 8) & 15]);
+        const int hi9 = max(max(hi4[k], hi4[(k + 4) & 15]), r[(k + 8) & 15]);
+        minOfMax = min(minOfMax, hi9);
+        maxOfMin = max(maxOfMin, lo9);
     }
-    return m - 1;
+    const int dark = v - minOfMax, bright = maxOfMin - v;
+    return (dark > bright ? dark : bright) - 1;
 }
 
 /* One CTA = one 35-px-grid cell of one level of one frame: cv::FAST(roi, iniTh) -> if empty cv::FAST(roi, minTh),
