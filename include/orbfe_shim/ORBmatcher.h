@@ -1,0 +1,85 @@
+/* ORBmatcher.h (orbfe shim) — the descriptor-matching core of ORB_SLAM3::ORBmatcher and Frame with the
+ * reference's signatures (/root/reference/include/ORBmatcher.h:35-111, include/Frame.h:114,304).
+ *
+ * Only the hot-path members are provided: the constants, the constructor, the static DescriptorDistance, the
+ * brute-force top-2 core that SearchByBoW's inner loops perform (src/ORBmatcher.cc:311-375, 870-908), and free
+ * functions carrying the bodies of Frame::ComputeStereoMatches / ComputeStereoFishEyeMatches's matching step.
+ * The projection / BoW-node gating around that core stays in the reference's ORBmatcher.cc. */
+#ifndef ORBFE_SHIM_ORBMATCHER_H
+#define ORBFE_SHIM_ORBMATCHER_H
+
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "ORBextractor.h"
+
+namespace ORB_SLAM3 {
+
+class ORBmatcher {
+public:
+    ORBmatcher(float nnratio = 0.6, bool checkOri = true) : mfNNratio(nnratio), mbCheckOrientation(checkOri) {}
+
+    /* src/ORBmatcher.cc:2591-2607.  One 256-bit pair: eight popcounts on the host — launching a kernel for 32 bytes
+     * would cost more than the answer; the batched form is orbfe_descriptor_distances(). */
+    static int DescriptorDistance(const cv::Mat& a, const cv::Mat& b) {
+        const uint32_t* pa = a.ptr<uint32_t>();
+        const uint32_t* pb = b.ptr<uint32_t>();
+        int dist = 0;
+        for (int i = 0; i < 8; i++) dist += __builtin_popcount(pa[i] ^ pb[i]);
+        return dist;
+    }
+
+    /* The top-2 core of SearchByBoW over whole descriptor matrices (rows x 32, CV_8U): for every query row the two
+     * smallest distances, the lowest best row, and the TH_LOW + mfNNratio verdict.  kfkf selects `best1 < TH_LOW`
+     * (src/ORBmatcher.cc:906) instead of `<=` (:373). */
+    int SearchTop2(const cv::Mat& queries, const cv::Mat& database, std::vector<orbfe_match>& out, bool kfkf = false, int device = 0) const {
+        out.resize(queries.rows);
+        std::vector<unsigned char> q((size_t)queries.rows * 32), db((size_t)database.rows * 32);
+        for (int i = 0; i < queries.rows; i++) std::memcpy(&q[(size_t)i * 32], queries.ptr<unsigned char>(i), 32);
+        for (int i = 0; i < database.rows; i++) std::memcpy(&db[(size_t)i * 32], database.ptr<unsigned char>(i), 32);
+        if (orbfe_hamming_top2(device, q.data(), queries.rows, db.data(), database.rows, TH_LOW, mfNNratio, kfkf ? 1 : 0, out.data()) != ORBFE_OK)
+            throw std::runtime_error(std::string("orbfe_hamming_top2: ") + orbfe_last_error());
+        int n = 0;
+        for (const orbfe_match& m : out) n += m.accepted;
+        return n;
+    }
+
+    static const int TH_LOW = 50;
+    static const int TH_HIGH = 100;
+    static const int HISTO_LENGTH = 30;
+
+protected:
+    float mfNNratio;
+    bool mbCheckOrientation;
+};
+
+/* Body of Frame::ComputeStereoMatches (src/Frame.cc:797-967) for the frames the two extractors processed last.
+ * mb is uninitialised in the reference when this runs (src/Frame.cc:827 vs :173); the intended maxD = mbf/mb = fx
+ * is therefore an explicit argument.  mvuRight / mvDepth are resized to N and filled (-1 = no match). */
+inline void ComputeStereoMatches(ORBextractor* left, ORBextractor* right, int N, float mbf, float fx,
+                                 std::vector<float>& mvuRight, std::vector<float>& mvDepth) {
+    mvuRight.assign(N, -1.0f);
+    mvDepth.assign(N, -1.0f);
+    if (N == 0) return;
+    if (orbfe_stereo_match_batch_device(left->Impl(), right->Impl(), 1, mbf, 0.0f, fx, nullptr) != ORBFE_OK)
+        throw std::runtime_error(std::string("orbfe_stereo_match: ") + orbfe_last_error());
+    int n = 0;
+    if (orbfe_stereo_result(left->Impl(), 0, mvuRight.data(), mvDepth.data(), N, &n) != ORBFE_OK)
+        throw std::runtime_error(std::string("orbfe_stereo_result: ") + orbfe_last_error());
+}
+
+/* Matching step of Frame::ComputeStereoFishEyeMatches (src/Frame.cc:1137-1144): knnMatch(k=2) + `d0 < d1*0.7`.
+ * match[i] = row of stereoDescRight or -1; triangulation of the survivors stays in KannalaBrandt8 (host). */
+inline void FishEyeKnnMatches(const cv::Mat& stereoDescLeft, const cv::Mat& stereoDescRight, std::vector<int>& match, int device = 0) {
+    match.assign(stereoDescLeft.rows, -1);
+    if (stereoDescLeft.rows == 0) return;
+    std::vector<unsigned char> q((size_t)stereoDescLeft.rows * 32), t((size_t)stereoDescRight.rows * 32);
+    for (int i = 0; i < stereoDescLeft.rows; i++) std::memcpy(&q[(size_t)i * 32], stereoDescLeft.ptr<unsigned char>(i), 32);
+    for (int i = 0; i < stereoDescRight.rows; i++) std::memcpy(&t[(size_t)i * 32], stereoDescRight.ptr<unsigned char>(i), 32);
+    if (orbfe_knn2_ratio(device, q.data(), stereoDescLeft.rows, t.data(), stereoDescRight.rows, 0.7, match.data(), nullptr, nullptr) != ORBFE_OK)
+        throw std::runtime_error(std::string("orbfe_knn2_ratio: ") + orbfe_last_error());
+}
+
+}  // namespace ORB_SLAM3
+#endif

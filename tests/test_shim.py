@@ -1,0 +1,42 @@
+"""The C++ drop-in shim (include/orbfe_shim): compiles as the reference's callers use it (CPU), and on a GPU
+produces the oracle's results when driven like Frame.cc drives ORBextractor / ComputeStereoMatches."""
+import os
+import re
+import subprocess
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+PKG = os.path.join(ROOT, "orb_slam3_detailed_comments_kor_b200")
+
+
+def test_shim_compiles_without_opencv():
+    subprocess.check_call(["g++", "-std=c++17", "-Wall", "-fsyntax-only", "-I" + os.path.join(ROOT, "include"),
+                           os.path.join(ROOT, "tests", "shim_smoke.cpp")])
+
+
+@pytest.mark.gpu
+def test_shim_matches_oracle(tmp_path):
+    from oracle import orb_oracle as O
+    from orb_slam3_detailed_comments_kor_b200 import synth
+    exe = str(tmp_path / "shim_smoke")
+    subprocess.check_call(["g++", "-std=c++17", "-O1", "-I" + os.path.join(ROOT, "include"), os.path.join(ROOT, "tests", "shim_smoke.cpp"),
+                           "-o", exe, "-L" + PKG, "-lorbfe", "-L" + os.path.join(PKG, "synth"), "-lsynth",
+                           "-Wl,-rpath," + PKG, "-Wl,-rpath," + os.path.join(PKG, "synth")])
+    out = subprocess.check_output([exe], text=True)
+    f = dict(re.findall(r"(\w+)=([-\d.x(),]+)", out))
+    params = (1200, 1.2, 8, 20, 7)
+    L, R = synth.stereo_pair(0, 752, 480)
+    oL, oR = O.OracleExtractor(*params), O.OracleExtractor(*params)
+    mono, kL, dL = oL(L)
+    monoR, kR, dR = oR(R)
+    kept, u, d = O.stereo_match(oL, oR, kL, dL, kR, dR, 47.90639, 0.0, 435.2047)
+    top2 = O.hamming_top2(dL, dR, 50, 0.9, False)
+    assert int(f["n"]) == len(kL) and int(f["mono"]) == mono and int(f["monoR"]) == monoR
+    assert f["pyr0"] == "752x480" and int(f["levels"]) == 8 and int(f["empty"]) == -1
+    assert int(f["stereo"]) == kept
+    assert int(f["d01"]) == O.descriptor_distance(dL[0], dL[1])
+    assert int(f["top2acc"]) == int(top2["accepted"].sum())
+    first = "(%.1f,%.1f,%.3f,%d)" % (kL[0]["x"], kL[0]["y"], kL[0]["angle"], kL[0]["octave"])
+    assert f["first"] == first
