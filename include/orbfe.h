@@ -159,6 +159,21 @@ int orbfe_matcher_top2_device(orbfe_matcher* m, const uint8_t* d_queries, int nq
  * reference is single-process. */
 int orbfe_top2_merge_device(int device, const orbfe_match* d_parts, int nshards, int nq, int th, float ratio,
                             int strict_lt, orbfe_match* d_out, void* stream);
+/* The top-2 search for callers that cannot allocate (no counterpart in the reference; it has no GPU memory to
+ * manage).  Meant for ORB-SLAM3's per-frame Tracking thread, which runs against a frame deadline while LocalMapping
+ * and LoopClosing use the same GPU: cudaMalloc/cudaFree lock the device and cudaFree waits for all of it, so that
+ * thread must not allocate; and for processes whose own pool has already taken all device memory, where an
+ * allocation would just fail.  Same inputs, outputs and results as orbfe_matcher_top2_device, but no object: the
+ * per-slice scratch is a fixed 4 MiB array inside the library image (each GPU that loads the library keeps it until
+ * exit).  Limits: nq <= 4096 (more is refused with ORBFE_E_CAPACITY); pointers are device pointers on `device`,
+ * 16-byte aligned; `stream` is used as given (NULL = the default stream).  The call performs no cudaMalloc/cudaFree
+ * and calls no allocating library routine.  The first call on each device looks up the array's device address
+ * (cudaGetSymbolAddress) — make that first call before starting any stream capture.  All calls on a device share the
+ * one array, which keeps whatever the last call wrote (nothing needs clearing: each call rewrites every record it
+ * reads); two calls whose kernels can overlap on the GPU (different streams, or different threads) race on it —
+ * keep them on one stream or otherwise ordered. */
+int orbfe_hamming_top2_static(int device, const uint8_t* d_queries, int nq, const uint8_t* d_db, int64_t ndb,
+                              int64_t index_base, int th, float ratio, int strict_lt, orbfe_match* d_out, void* stream);
 /* One-shot convenience over host memory (creates and destroys a matcher). */
 int orbfe_hamming_top2(int device, const uint8_t* q, int nq, const uint8_t* db, int64_t ndb, int th, float ratio,
                        int strict_lt, orbfe_match* out);

@@ -64,6 +64,7 @@ SIGNATURES = {
     "orbfe_matcher_top2": (i32, [vp, vp, i32, i32, f32, i32, vp]),
     "orbfe_matcher_top2_device": (i32, [vp, vp, i32, i32, f32, i32, vp, vp]),
     "orbfe_top2_merge_device": (i32, [i32, vp, i32, i32, i32, f32, i32, vp, vp]),
+    "orbfe_hamming_top2_static": (i32, [i32, vp, i32, vp, i64, i64, i32, f32, i32, vp, vp]),
     "orbfe_hamming_top2": (i32, [i32, vp, i32, vp, i64, i32, f32, i32, vp]),
     "orbfe_knn2_ratio": (i32, [i32, vp, i32, vp, i32, f64, vp, vp, vp]),
 }

@@ -532,3 +532,53 @@ int orbfe_descriptor_distances(int device, const uint8_t* a, const uint8_t* b, i
 }
 
 }  /* extern "C" */
+
+/* ------------------------------------------------------------------------- top-2 search without any allocation */
+/* orbfe_hamming_top2_static: the same top-2 search as orbfe_matcher_top2_device for callers that must not, or
+ * cannot, allocate device memory.  In ORB-SLAM3 terms that is the per-frame Tracking thread: it has a frame-period
+ * deadline and shares the GPU with the LocalMapping and LoopClosing threads, while cudaMalloc/cudaFree take a
+ * device-wide lock and cudaFree waits for the whole device — an allocation on that thread stalls the others.  It is
+ * also any host process whose memory pool already owns all of the device memory, where cudaMalloc simply fails.
+ * The search needs scratch memory (one partial top-2 record per (database slice, query)); here that scratch is a
+ * fixed array that lives in the library image instead of being allocated: 64 slices x 4096 queries x 16 bytes
+ * = 4 MiB, held by every GPU that loads liborbfe.so until the process exits.
+ *
+ * g_static_parts is a device symbol.  In host code its name is only a stand-in, not a device address, so the
+ * launch code below never passes it to a kernel directly: once per device, with that device current, it asks the
+ * runtime for the real address (cudaGetSymbolAddress) and caches it. */
+#define ORBFE_STATIC_MAX_QUERIES 4096
+#define ORBFE_STATIC_MAX_SLICES 64
+static __device__ __align__(256) orbfe_match g_static_parts[(size_t)ORBFE_STATIC_MAX_SLICES * ORBFE_STATIC_MAX_QUERIES];
+
+#include <mutex>
+static std::mutex g_static_mu;
+static orbfe_match* g_static_addr[64]; /* per device ordinal, filled on first use */
+
+extern "C" int orbfe_hamming_top2_static(int device, const uint8_t* d_queries, int nq, const uint8_t* d_db, int64_t ndb,
+                                         int64_t index_base, int th, float ratio, int strict_lt, orbfe_match* d_out, void* stream) {
+    if (!d_queries || !d_out || nq < 1 || ndb < 0 || (ndb > 0 && !d_db)) { orbfe_set_error("bad argument"); return ORBFE_E_INVALID; }
+    if (nq > ORBFE_STATIC_MAX_QUERIES) {
+        orbfe_set_error("orbfe_hamming_top2_static: %d queries exceed the built-in scratch (max %d); use orbfe_matcher_top2_device", nq,
+                        ORBFE_STATIC_MAX_QUERIES);
+        return ORBFE_E_CAPACITY;
+    }
+    if ((((uintptr_t)d_queries) | ((uintptr_t)d_db)) & 15) { orbfe_set_error("query/database pointers must be 16-byte aligned"); return ORBFE_E_INVALID; }
+    if (device < 0 || device >= 64) { orbfe_set_error("device ordinal %d out of range", device); return ORBFE_E_INVALID; }
+    ORBFE_CUDA(cudaSetDevice(device));
+    orbfe_match* parts = nullptr;
+    {
+        std::lock_guard<std::mutex> lk(g_static_mu);
+        if (!g_static_addr[device]) {
+            /* first call on this device: resolve the symbol's address here, with `device` current */
+            orbfe_match* p = nullptr;
+            ORBFE_CUDA(cudaGetSymbolAddress((void**)&p, g_static_parts));
+            g_static_addr[device] = p;
+        }
+        parts = g_static_addr[device];
+    }
+    /* Every (slice, query) record the merge reads is written by the search kernel of the same call, so nothing in
+     * the shared array has to start at zero and nothing is cleared; what a previous call left behind is overwritten
+     * or never read. */
+    return launch_top2(d_queries, nq, d_db, ndb, index_base, parts, ORBFE_STATIC_MAX_SLICES, th, ratio, 0.0, strict_lt ? 1 : 0, d_out,
+                       (cudaStream_t)stream);
+}
