@@ -27,23 +27,25 @@ static __device__ __forceinline__ int reflect101(int p, int n) {
 }
 
 /* ------------------------------------------------------------------------------------------------ pyramid */
-/* One thread = one 16-byte chunk of one padded output row.  Border bytes are recomputed through the
- * reflected interior coordinate, so resize and copyMakeBorder are one pass with 128-bit stores only. */
-__global__ void __launch_bounds__(256) k_pyramid_level(const __grid_constant__ ExDesc d, ExBuffers b,
-                                                       const uint8_t* __restrict__ input, int level) {
-    const LevelDesc& L = d.lv[level];
+/* Level 0: copyMakeBorder(image, 19, REFLECT_101) (src/ORBextractor.cc:1170-1173).  One thread = one 16-byte chunk
+ * of a padded row; chunks that lie inside the image and are 16-byte aligned in the source move as one 128-bit
+ * load/store, the others (borders, odd widths) go byte by byte through the reflected coordinate. */
+__global__ void __launch_bounds__(256) k_pyramid_copy0(const __grid_constant__ ExDesc d, ExBuffers b, const uint8_t* __restrict__ input) {
+    const LevelDesc& L = d.lv[0];
     const int chunks = L.pitch >> 4;
     const int rows = L.h + 2 * ORBFE_EDGE;
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= chunks * rows) return;
     const int row = idx / chunks, chunk = idx - row * chunks;
     const size_t f = blockIdx.y;
-    uint8_t* slab = b.pyr + f * d.pyrSlab;
     const int yi = reflect101(row - ORBFE_EDGE, L.h);
-    uint32_t out[4] = {0, 0, 0, 0};
     const int px0 = chunk * 16 - ORBFE_ROW_LEAD;
-    if (level == 0) {
-        const uint8_t* src = input + f * (size_t)d.W * d.H + (size_t)yi * d.W;
+    const uint8_t* src = input + f * (size_t)d.W * d.H + (size_t)yi * d.W;
+    uint4 o;
+    if (px0 >= 0 && px0 + 16 <= L.w && ((reinterpret_cast<uintptr_t>(src + px0) & 15) == 0)) {
+        o = __ldg(reinterpret_cast<const uint4*>(src + px0));
+    } else {
+        uint32_t out[4] = {0, 0, 0, 0};
 #pragma unroll
         for (int k = 0; k < 16; k++) {
             const int px = px0 + k;
@@ -51,89 +53,140 @@ __global__ void __launch_bounds__(256) k_pyramid_level(const __grid_constant__ E
             if (px >= -ORBFE_EDGE && px < L.w + ORBFE_EDGE) v = __ldg(src + reflect101(px, L.w));
             out[k >> 2] |= v << (8 * (k & 3));
         }
-    } else {
-        const LevelDesc& P = d.lv[level - 1];
-        const uint8_t* sint = slab + P.pyrOff + (size_t)ORBFE_EDGE * P.pitch + ORBFE_ROW_LEAD;
-        const uint2 yt = __ldg(b.tabs + L.tabY + yi);
-        /* row yt.x+1 and column sx+1 may be the source's own border: their coefficient is then 0 */
-        const uint8_t* r0 = sint + (size_t)yt.x * P.pitch;
-        const uint8_t* r1 = r0 + P.pitch;
-        const int b0 = yt.y & 0xFFFF, b1 = yt.y >> 16;
+        o = make_uint4(out[0], out[1], out[2], out[3]);
+    }
+    *reinterpret_cast<uint4*>(b.pyr + f * d.pyrSlab + L.pyrOff + (size_t)row * L.pitch + chunk * 16) = o;
+}
+
+/* Levels >= 1: cv::resize(INTER_LINEAR) from the level below + copyMakeBorder in one pass
+ * (src/ORBextractor.cc:1163-1168).  One thread = four adjacent output pixels (one 32-bit store, lanes adjacent, so
+ * a warp writes 128 contiguous bytes).  Interior groups fetch each source row as three aligned words, funnel-shift
+ * them to the first tap, and form every horizontal tap pair with one PRMT + one DP2A
+ * (c0*S[sx] + c1*S[sx+1], 16-bit coefficients x 8-bit pixels); groups that touch the border recompute the reflected
+ * interior pixel byte-wise.  Arithmetic is OpenCV's 11-bit fixed point. */
+static __device__ __forceinline__ uint32_t resize_px_generic(const uint8_t* r0, const uint8_t* r1, uint2 xt, int b0, int b1) {
+    const int c0 = xt.y & 0xFFFF, c1 = xt.y >> 16;
+    const int h0 = r0[xt.x] * c0 + r0[xt.x + 1] * c1;
+    const int h1 = r1[xt.x] * c0 + r1[xt.x + 1] * c1;
+    return (uint32_t)((((b0 * (h0 >> 4)) >> 16) + ((b1 * (h1 >> 4)) >> 16) + 2) >> 2);
+}
+
+__global__ void __launch_bounds__(256) k_pyramid_level(const __grid_constant__ ExDesc d, ExBuffers b, int level) {
+    const LevelDesc& L = d.lv[level];
+    const LevelDesc& P = d.lv[level - 1];
+    const int groups = L.pitch >> 2;
+    const int rows = L.h + 2 * ORBFE_EDGE;
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= groups * rows) return;
+    const int row = idx / groups, g = idx - row * groups;
+    const size_t f = blockIdx.y;
+    uint8_t* slab = b.pyr + f * d.pyrSlab;
+    const int yi = reflect101(row - ORBFE_EDGE, L.h);
+    const uint8_t* sint = slab + P.pyrOff + (size_t)ORBFE_EDGE * P.pitch + ORBFE_ROW_LEAD;
+    const uint2 yt = __ldg(b.tabs + L.tabY + yi);
+    /* row yt.x+1 and column sx+1 may be the source's own border: their coefficient is then 0 */
+    const uint8_t* r0 = sint + (size_t)yt.x * P.pitch;
+    const uint8_t* r1 = r0 + P.pitch;
+    const int b0 = yt.y & 0xFFFF, b1 = yt.y >> 16;
+    const int px0 = g * 4 - ORBFE_ROW_LEAD;
+    uint32_t out = 0;
+    if (px0 >= 0 && px0 + 4 <= L.w) {
+        const uint4* tp = reinterpret_cast<const uint4*>(b.tabs + L.tabX + px0); /* tabX is 4-entry aligned */
+        const uint4 ta = __ldg(tp), tb = __ldg(tp + 1); /* entries (sx, c0|c1<<16) of the four pixels */
+        const uint32_t sx0 = ta.x;
+        const uint32_t base = sx0 & ~3u, sh = (sx0 & 3u) * 8;
+        const uint32_t* q0 = reinterpret_cast<const uint32_t*>(r0 + base);
+        const uint32_t* q1 = reinterpret_cast<const uint32_t*>(r1 + base);
+        const uint32_t a0 = q0[0], a1 = q0[1], a2 = q0[2], c0w = q1[0], c1w = q1[1], c2w = q1[2];
+        const uint32_t u0 = __funnelshift_r(a0, a1, sh), u1 = __funnelshift_r(a1, a2, sh); /* bytes sx0 .. sx0+7 of row 0 */
+        const uint32_t v0 = __funnelshift_r(c0w, c1w, sh), v1 = __funnelshift_r(c1w, c2w, sh);
+        const uint32_t sxs[4] = {ta.x, ta.z, tb.x, tb.z};
+        const uint32_t cfs[4] = {ta.y, ta.w, tb.y, tb.w};
 #pragma unroll
-        for (int k = 0; k < 16; k++) {
+        for (int k = 0; k < 4; k++) {
+            const uint32_t off = sxs[k] - sx0;            /* 0..4: 1.2x downscale keeps four taps within 6 bytes */
+            const uint32_t sel = off * 0x11u + 0x10u;     /* bytes (off, off+1) -> low half */
+            const uint32_t h0 = __dp2a_lo(cfs[k], __byte_perm(u0, u1, sel), 0u);
+            const uint32_t h1 = __dp2a_lo(cfs[k], __byte_perm(v0, v1, sel), 0u);
+            const uint32_t v = (uint32_t)((((b0 * (int)(h0 >> 4)) >> 16) + ((b1 * (int)(h1 >> 4)) >> 16) + 2) >> 2);
+            out |= v << (8 * k);
+        }
+    } else {
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
             const int px = px0 + k;
-            uint32_t v = 0;
-            if (px >= -ORBFE_EDGE && px < L.w + ORBFE_EDGE) {
-                const uint2 xt = __ldg(b.tabs + L.tabX + reflect101(px, L.w));
-                const int c0 = xt.y & 0xFFFF, c1 = xt.y >> 16;
-                const int h0 = r0[xt.x] * c0 + r0[xt.x + 1] * c1;
-                const int h1 = r1[xt.x] * c0 + r1[xt.x + 1] * c1;
-                v = (uint32_t)((((b0 * (h0 >> 4)) >> 16) + ((b1 * (h1 >> 4)) >> 16) + 2) >> 2);
-            }
-            out[k >> 2] |= v << (8 * (k & 3));
+            if (px >= -ORBFE_EDGE && px < L.w + ORBFE_EDGE)
+                out |= resize_px_generic(r0, r1, __ldg(b.tabs + L.tabX + reflect101(px, L.w)), b0, b1) << (8 * k);
         }
     }
-    *reinterpret_cast<uint4*>(slab + L.pyrOff + (size_t)row * L.pitch + chunk * 16) = make_uint4(out[0], out[1], out[2], out[3]);
+    *reinterpret_cast<uint32_t*>(slab + L.pyrOff + (size_t)row * L.pitch + g * 4) = out;
 }
 
 /* --------------------------------------------------------------------------------------------------- blur */
-/* 7x7 sigma-2 Gaussian as OpenCV's 8U fixed point: taps {18,34,48,56,48,34,18}/256 horizontally (Q8.8, kept
- * exact in 16 bits), the same vertically (Q16.16), + 2^15 >> 16.  The padded pyramid already holds the
- * REFLECT_101 border, so the tile load needs no edge logic. */
+/* 7x7 sigma-2 Gaussian as OpenCV's 8U fixed point: taps {18,34,48,56,48,34,18}/256 horizontally (Q8.8, exact in
+ * 16 bits), the same vertically (Q16.16), + 2^15 >> 16.  The padded pyramid already holds the REFLECT_101 border,
+ * so no edge logic.  Horizontal pass: the 7 taps of a pixel are two DP4A on funnel-shifted source words.  Its results
+ * are stored as vertically adjacent 16-bit pairs (rows 2j, 2j+1 of the tile in one 32-bit word), so the vertical
+ * pass is four DP2A (16-bit x 8-bit pairs) per pixel and one thread produces a 4 x 2 block from five 128-bit loads. */
 #define BLUR_TW 64
 #define BLUR_TH 32
+#define BLUR_PAIRS (BLUR_TH / 2 + 4)   /* tile rows y0-4 .. y0+TH+3 as pairs */
 __global__ void __launch_bounds__(256) k_blur7(const __grid_constant__ ExDesc d, ExBuffers b, int level) {
-    __shared__ uint32_t s_src[BLUR_TH + 6][18];
-    __shared__ __align__(8) uint16_t s_h[BLUR_TH + 6][BLUR_TW];
+    __shared__ __align__(16) uint32_t s_h[BLUR_PAIRS][BLUR_TW];
     const LevelDesc& L = d.lv[level];
     const size_t f = blockIdx.z;
     const int x0 = blockIdx.x * BLUR_TW, y0 = blockIdx.y * BLUR_TH;
     const uint8_t* pad = b.pyr + f * d.pyrSlab + L.pyrOff;
-    for (int i = threadIdx.x; i < (BLUR_TH + 6) * 18; i += 256) {
-        const int r = i / 18, c = i - r * 18;
-        int gy = y0 - 3 + r;
-        gy = min(gy, L.h + ORBFE_EDGE - 1);
-        const uint8_t* p = pad + (size_t)(gy + ORBFE_EDGE) * L.pitch + ORBFE_ROW_LEAD + x0 - 4 + 4 * c;
-        s_src[r][c] = *reinterpret_cast<const uint32_t*>(p);
-    }
-    __syncthreads();
-    for (int i = threadIdx.x; i < (BLUR_TH + 6) * 16; i += 256) {
-        const int r = i >> 4, q = i & 15;
-        const uint32_t w0 = s_src[r][q], w1 = s_src[r][q + 1], w2 = s_src[r][q + 2];
-        int v[10];
-        v[0] = (w0 >> 8) & 0xFF; v[1] = (w0 >> 16) & 0xFF; v[2] = w0 >> 24;
-        v[3] = w1 & 0xFF; v[4] = (w1 >> 8) & 0xFF; v[5] = (w1 >> 16) & 0xFF; v[6] = w1 >> 24;
-        v[7] = w2 & 0xFF; v[8] = (w2 >> 8) & 0xFF; v[9] = (w2 >> 16) & 0xFF;
-        uint32_t o[4];
+    const uint32_t KLO = 18u | (34u << 8) | (48u << 16) | (56u << 24);  /* taps -3..0 */
+    const uint32_t KHI = 48u | (34u << 8) | (18u << 16);                /* taps +1..+3 */
+    const int ymax = L.h + ORBFE_EDGE - 1;
+    for (int i = threadIdx.x; i < BLUR_PAIRS * (BLUR_TW / 4); i += 256) {
+        const int j = i >> 4, q = i & 15;                 /* row pair j, pixel group q (4 px) */
+        uint32_t hrow[2][4];
 #pragma unroll
-        for (int j = 0; j < 4; j++)
-            o[j] = 18 * (v[j] + v[j + 6]) + 34 * (v[j + 1] + v[j + 5]) + 48 * (v[j + 2] + v[j + 4]) + 56 * v[j + 3];
-        *reinterpret_cast<uint2*>(&s_h[r][4 * q]) = make_uint2(o[0] | (o[1] << 16), o[2] | (o[3] << 16));
+        for (int rr = 0; rr < 2; rr++) {
+            const int gy = min(y0 - 4 + 2 * j + rr, ymax);
+            const uint32_t* p = reinterpret_cast<const uint32_t*>(pad + (size_t)(gy + ORBFE_EDGE) * L.pitch + ORBFE_ROW_LEAD + x0 + 4 * q - 4);
+            const uint32_t w0 = __ldg(p), w1 = __ldg(p + 1), w2 = __ldg(p + 2);   /* px x-4..x-1 | x..x+3 | x+4..x+7 */
+            hrow[rr][0] = __dp4a(__funnelshift_r(w0, w1, 8), KLO, __dp4a(__funnelshift_r(w1, w2, 8), KHI, 0u));
+            hrow[rr][1] = __dp4a(__funnelshift_r(w0, w1, 16), KLO, __dp4a(__funnelshift_r(w1, w2, 16), KHI, 0u));
+            hrow[rr][2] = __dp4a(__funnelshift_r(w0, w1, 24), KLO, __dp4a(__funnelshift_r(w1, w2, 24), KHI, 0u));
+            hrow[rr][3] = __dp4a(w1, KLO, __dp4a(w2, KHI, 0u));
+        }
+        *reinterpret_cast<uint4*>(&s_h[j][4 * q]) = make_uint4(hrow[0][0] | (hrow[1][0] << 16), hrow[0][1] | (hrow[1][1] << 16),
+                                                               hrow[0][2] | (hrow[1][2] << 16), hrow[0][3] | (hrow[1][3] << 16));
     }
     __syncthreads();
     uint8_t* dst = b.blur + f * d.blurSlab + L.blurOff;
-    for (int i = threadIdx.x; i < BLUR_TH * 16; i += 256) {
-        const int r = i >> 4, q = i & 15;
-        const int gy = y0 + r, gx = x0 + 4 * q;
-        if (gy >= L.h || gx >= L.bpitch) continue;
-        uint32_t acc[4] = {0, 0, 0, 0};
-        const int K[7] = {18, 34, 48, 56, 48, 34, 18};
+    /* one item = output rows (y0+2m, y0+2m+1) x 4 pixels; needs pairs m .. m+4 (rows y0+2m-4 .. y0+2m+5) */
+    const int m = threadIdx.x >> 4, q = threadIdx.x & 15;
+    const int gy = y0 + 2 * m, gx = x0 + 4 * q;
+    if (gy < L.h && gx < L.bpitch) {
+        uint4 pr[5];
 #pragma unroll
-        for (int k = 0; k < 7; k++) {
-            const uint2 hv = *reinterpret_cast<const uint2*>(&s_h[r + k][4 * q]);
-            acc[0] += K[k] * (hv.x & 0xFFFF); acc[1] += K[k] * (hv.x >> 16);
-            acc[2] += K[k] * (hv.y & 0xFFFF); acc[3] += K[k] * (hv.y >> 16);
+        for (int k = 0; k < 5; k++) pr[k] = *reinterpret_cast<const uint4*>(&s_h[m + k][4 * q]);
+        /* even row y: rows y-3..y+3 = (pair0.hi) (pair1) (pair2) (pair3); odd row y+1: (pair1) (pair2) (pair3) (pair4.lo) */
+        const uint32_t E0 = 18u << 8, E1 = 34u | (48u << 8), E2 = 56u | (48u << 8), E3 = 34u | (18u << 8);
+        const uint32_t O1 = 18u | (34u << 8), O2 = 48u | (56u << 8), O3 = 48u | (34u << 8), O4 = 18u;
+        uint32_t oe = 0, oo = 0;
+        const uint32_t* P0 = &pr[0].x; const uint32_t* P1 = &pr[1].x; const uint32_t* P2 = &pr[2].x;
+        const uint32_t* P3 = &pr[3].x; const uint32_t* P4 = &pr[4].x;
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const uint32_t ve = __dp2a_lo(P0[k], E0, __dp2a_lo(P1[k], E1, __dp2a_lo(P2[k], E2, __dp2a_lo(P3[k], E3, 32768u))));
+            const uint32_t vo = __dp2a_lo(P1[k], O1, __dp2a_lo(P2[k], O2, __dp2a_lo(P3[k], O3, __dp2a_lo(P4[k], O4, 32768u))));
+            oe |= (ve >> 16) << (8 * k);
+            oo |= (vo >> 16) << (8 * k);
         }
-        const uint32_t o = ((acc[0] + 32768) >> 16) | (((acc[1] + 32768) >> 16) << 8) |
-                           (((acc[2] + 32768) >> 16) << 16) | (((acc[3] + 32768) >> 16) << 24);
-        *reinterpret_cast<uint32_t*>(dst + (size_t)gy * L.bpitch + gx) = o;
+        *reinterpret_cast<uint32_t*>(dst + (size_t)gy * L.bpitch + gx) = oe;
+        if (gy + 1 < L.h) *reinterpret_cast<uint32_t*>(dst + (size_t)(gy + 1) * L.bpitch + gx) = oo;
     }
 }
 
 /* --------------------------------------------------------------------------------------------------- FAST */
 #define FAST_TP 80   /* smem tile pitch: ROI width <= 76 (wCell <= 70, +6) + 3 bytes of alignment lead */
 #define FAST_RH 76
-#define FAST_NT 256
+#define FAST_NT 128
 /* ring offsets of cv::FAST 9/16: (dx,dy) for k = 0..15 */
 #define RING_OFF(k, TP)                                                                              \
     ((k) == 0 ? 3 * TP : (k) == 1 ? 3 * TP + 1 : (k) == 2 ? 2 * TP + 2 : (k) == 3 ? TP + 3 : (k) == 4 ? 3 : \
@@ -197,15 +250,32 @@ static __host__ __device__ __forceinline__ int fast_score(const uint8_t* c) {
     return (dark > bright ? dark : bright) - 1;
 }
 
+/* Sieve for four horizontally adjacent pixels at once (one 32-bit word of the tile): with a = |I(x,y+3) - I|,
+ * b = |I(x,y-3) - I|, r = |I(x+3,y) - I|, l = |I(x-3,y) - I| (VABSDIFF4, one instruction per four pixels), a corner at
+ * threshold t needs (a > t or b > t) and (r > t or l > t): every 9-arc of the ring holds one pixel of each opposite
+ * pair.  Returns bit 7 of byte k set iff pixel k passes.  gt(x) = bytes of x that exceed t, exact per byte (t <= 127). */
+static __device__ __forceinline__ uint32_t fast_sieve4(uint32_t c, uint32_t top, uint32_t bot, uint32_t lft, uint32_t rgt, uint32_t k127mt) {
+    const uint32_t a = __vabsdiffu4(top, c), b = __vabsdiffu4(bot, c), r = __vabsdiffu4(rgt, c), l = __vabsdiffu4(lft, c);
+    const uint32_t ga = ((a & 0x7F7F7F7Fu) + k127mt) | a, gb = ((b & 0x7F7F7F7Fu) + k127mt) | b;
+    const uint32_t gr = ((r & 0x7F7F7F7Fu) + k127mt) | r, gl = ((l & 0x7F7F7F7Fu) + k127mt) | l;
+    return (ga | gb) & (gr | gl) & 0x80808080u;
+}
+
+#define FAST_LISTCAP (70 * 70)
 /* One CTA = one 35-px-grid cell of one level of one frame: cv::FAST(roi, iniTh) -> if empty cv::FAST(roi, minTh),
  * with NMS seeing only this cell's scores at the current threshold (SURVEY.md §7 hard part 2).
+ * Work is funnelled through compacted lists so that each stage runs dense:
+ *   sieve (4 px per thread-step, all candidates) -> list1 -> exact 9-of-16 test -> list2 -> score -> NMS -> bitmask.
  * Output: the cell's keypoints in (y, x) order, packed, at the cell's slot range. */
-__global__ void __launch_bounds__(FAST_NT) k_fast_cells(const __grid_constant__ ExDesc d, ExBuffers b) {
-    __shared__ __align__(16) uint8_t s_img[FAST_RH * FAST_TP];
-    __shared__ __align__(16) uint8_t s_score[FAST_RH * FAST_TP];
-    __shared__ uint16_t s_list[70 * 70];
-    __shared__ uint32_t s_mask[(70 * 70 + 31) / 32 + 1];
-    __shared__ int s_nlist, s_total;
+__global__ void __launch_bounds__(FAST_NT, 8) k_fast_cells(const __grid_constant__ ExDesc d, ExBuffers b) {
+    /* dynamic smem, sized for the largest cell of this extractor: tile | score tile | list1 | list2 | mask */
+    extern __shared__ __align__(16) uint8_t s_dyn[];
+    uint8_t* s_img = s_dyn;
+    uint8_t* s_score = s_img + d.fastRows * FAST_TP;
+    uint16_t* s_list1 = reinterpret_cast<uint16_t*>(s_score + d.fastRows * FAST_TP);
+    uint16_t* s_list2 = s_list1 + d.fastPix;
+    uint32_t* s_mask = reinterpret_cast<uint32_t*>(s_list2 + d.fastPix);
+    __shared__ int s_n1, s_n2, s_total;
     __shared__ int s_wsum[FAST_NT / 32];
 
     const CellDesc cell = b.cells[blockIdx.x];
@@ -223,59 +293,105 @@ __global__ void __launch_bounds__(FAST_NT) k_fast_cells(const __grid_constant__ 
         const int nw = (ox + cell.rw + 3) >> 2;
         for (int i = threadIdx.x; i < cell.rh * nw; i += FAST_NT) {
             const int r = i / nw, c = i - r * nw;
-            reinterpret_cast<uint32_t*>(s_img + r * FAST_TP)[c] = *reinterpret_cast<const uint32_t*>(g + (size_t)r * L.pitch + 4 * c);
+            reinterpret_cast<uint32_t*>(s_img + r * FAST_TP)[c] = __ldg(reinterpret_cast<const uint32_t*>(g + (size_t)r * L.pitch + 4 * c));
         }
-        for (int i = threadIdx.x; i < FAST_RH * FAST_TP / 4; i += FAST_NT) reinterpret_cast<uint32_t*>(s_score)[i] = 0;
+        for (int i = threadIdx.x; i < cell.rh * (FAST_TP / 16); i += FAST_NT) reinterpret_cast<uint4*>(s_score)[i] = make_uint4(0, 0, 0, 0);
     }
     const int npix = cw * ch;
     const int nwords = (npix + 31) >> 5;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t invcw = (16777216u + cw - 1) / cw; /* p / cw == (p * invcw) >> 24 for p < 70*70 */
+    /* candidate columns are tile columns [cx0, cx0+cw); the sieve walks the tile words that overlap them */
+    const int cx0 = ox + 3, w0 = cx0 >> 2, ngw = ((cx0 + cw - 1) >> 2) - w0 + 1;
+    const uint32_t invgw = (16777216u + ngw - 1) / ngw;
+    const int nitems = ch * ngw;
     int th = d.iniTh;
     for (int pass = 0; pass < 2; pass++) {
-        if (threadIdx.x == 0) s_nlist = 0;
+        if (threadIdx.x == 0) { s_n1 = 0; s_n2 = 0; }
         for (int i = threadIdx.x; i < nwords; i += FAST_NT) s_mask[i] = 0;
         __syncthreads();
-        /* 1. threshold test on every candidate pixel; corners are queued so the expensive score is dense work */
-        for (int p0 = 0; p0 < npix; p0 += FAST_NT) {
-            const int p = p0 + threadIdx.x;
+        /* 1. sieve */
+        const uint32_t k127mt = (uint32_t)(127 - th) * 0x01010101u;
+        for (int i0 = 0; i0 < nitems; i0 += FAST_NT) {
+            const int i = i0 + threadIdx.x;
+            uint32_t hit = 0;
+            int r = 0, col0 = 0;
+            if (i < nitems) {
+                r = (int)(((uint32_t)i * invgw) >> 24);
+                const int wi = w0 + (i - r * ngw);
+                const uint32_t* row = reinterpret_cast<const uint32_t*>(s_img + (r + 3) * FAST_TP);
+                const uint32_t c = row[wi], lw = row[wi - 1], rw = row[wi + 1];
+                const uint32_t top = row[wi + 3 * (FAST_TP / 4)], bot = row[wi - 3 * (FAST_TP / 4)];
+                hit = fast_sieve4(c, top, bot, __byte_perm(lw, c, 0x4321), __byte_perm(c, rw, 0x6543), k127mt);
+                col0 = 4 * wi - cx0; /* candidate x of byte 0 (may be negative at the left edge) */
+                /* drop lanes outside [0, cw) */
+#pragma unroll
+                for (int k = 0; k < 4; k++)
+                    if (col0 + k < 0 || col0 + k >= cw) hit &= ~(0x80u << (8 * k));
+            }
+            const int cnt = __popc(hit);
+            int incl = cnt;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+                if (lane >= o) incl += t;
+            }
+            const int wtot = __shfl_sync(0xFFFFFFFFu, incl, 31);
+            if (wtot) {
+                int base = 0;
+                if (lane == 31) base = atomicAdd(&s_n1, wtot);
+                base = __shfl_sync(0xFFFFFFFFu, base, 31) + incl - cnt;
+#pragma unroll
+                for (int k = 0; k < 4; k++)
+                    if (hit & (0x80u << (8 * k))) s_list1[base++] = (uint16_t)(r * cw + col0 + k);
+            }
+        }
+        __syncthreads();
+        const int n1 = s_n1;
+        /* 2. exact test on the sieve's survivors */
+        for (int e0 = 0; e0 < n1; e0 += FAST_NT) {
+            const int e = e0 + threadIdx.x;
             bool isc = false;
-            if (p < npix) {
-                const int py = p / cw, px = p - py * cw;
-                isc = fast_is_corner(s_img + (py + 3) * FAST_TP + ox + px + 3, th);
+            int p = 0;
+            if (e < n1) {
+                p = s_list1[e];
+                const int py = (int)(((uint32_t)p * invcw) >> 24), px = p - py * cw;
+                isc = fast_is_corner(s_img + (py + 3) * FAST_TP + cx0 + px, th);
             }
             const uint32_t bal = __ballot_sync(0xFFFFFFFFu, isc);
             if (bal) {
                 int base = 0;
-                if (lane == 0) base = atomicAdd(&s_nlist, __popc(bal));
+                if (lane == 0) base = atomicAdd(&s_n2, __popc(bal));
                 base = __shfl_sync(0xFFFFFFFFu, base, 0);
-                if (isc) s_list[base + __popc(bal & ((1u << lane) - 1))] = (uint16_t)p;
+                if (isc) s_list2[base + __popc(bal & ((1u << lane) - 1))] = (uint16_t)p;
             }
         }
         __syncthreads();
-        const int nl = s_nlist;
-        /* 2. scores */
-        for (int e = threadIdx.x; e < nl; e += FAST_NT) {
-            const int p = s_list[e];
-            const int py = p / cw, px = p - py * cw;
-            const int o = (py + 3) * FAST_TP + ox + px + 3;
+        const int n2 = s_n2;
+        /* 3. scores */
+        for (int e = threadIdx.x; e < n2; e += FAST_NT) {
+            const int p = s_list2[e];
+            const int py = (int)(((uint32_t)p * invcw) >> 24), px = p - py * cw;
+            const int o = (py + 3) * FAST_TP + cx0 + px;
             s_score[o] = (uint8_t)fast_score(s_img + o);
         }
         __syncthreads();
-        /* 3. non-maximum suppression: strictly greater than the 8 neighbours (non-corners count 0) */
-        for (int e = threadIdx.x; e < nl; e += FAST_NT) {
-            const int p = s_list[e];
-            const int py = p / cw, px = p - py * cw;
-            const uint8_t* s = s_score + (py + 3) * FAST_TP + ox + px + 3;
-            const int v = s[0];
-            const int nb = max(max(max(s[-FAST_TP - 1], s[-FAST_TP]), max(s[-FAST_TP + 1], s[-1])),
-                               max(max(s[1], s[FAST_TP - 1]), max(s[FAST_TP], s[FAST_TP + 1])));
+        /* 4. non-maximum suppression: strictly greater than the 8 neighbours (non-corners count 0) */
+        for (int e = threadIdx.x; e < n2; e += FAST_NT) {
+            const int p = s_list2[e];
+            const int py = (int)(((uint32_t)p * invcw) >> 24), px = p - py * cw;
+            const uint8_t* sc = s_score + (py + 3) * FAST_TP + cx0 + px;
+            const int v = sc[0];
+            const int nb = max(max(max((int)sc[-FAST_TP - 1], (int)sc[-FAST_TP]), max((int)sc[-FAST_TP + 1], (int)sc[-1])),
+                               max(max((int)sc[1], (int)sc[FAST_TP - 1]), max((int)sc[FAST_TP], (int)sc[FAST_TP + 1])));
             if (v > nb) atomicOr(&s_mask[p >> 5], 1u << (p & 31));
         }
         __syncthreads();
-        /* 4. ordered count: exclusive prefix over the mask words (row-major = (y,x) order) */
+        /* 5. ordered count: each thread owns a contiguous run of mask words, so thread order = (y,x) order */
+        const int per = (nwords + FAST_NT - 1) / FAST_NT;
+        const int wbeg = min((int)threadIdx.x * per, nwords), wend = min(wbeg + per, nwords);
         int mine = 0;
-        for (int i = threadIdx.x; i < nwords; i += FAST_NT) mine += __popc(s_mask[i]);
-        /* nwords <= 154 < FAST_NT, so each thread owns at most one word: prefix over threads */
+        for (int i = wbeg; i < wend; i++) mine += __popc(s_mask[i]);
         int incl = mine;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
@@ -290,16 +406,16 @@ __global__ void __launch_bounds__(FAST_NT) k_fast_cells(const __grid_constant__ 
         __syncthreads();
         const int total = s_total;
         if (total > 0 || pass == 1) {
-            if (threadIdx.x < nwords) {
-                uint32_t m = s_mask[threadIdx.x];
-                int k = wbase + incl - mine;
-                uint32_t* out = b.cand + f * d.candCap + cell.candBase;
+            int k = wbase + incl - mine;
+            uint32_t* out = b.cand + f * d.candCap + cell.candBase;
+            for (int i = wbeg; i < wend; i++) {
+                uint32_t m = s_mask[i];
                 while (m) {
                     const int bit = __ffs(m) - 1;
                     m &= m - 1;
-                    const int p = threadIdx.x * 32 + bit;
-                    const int py = p / cw, px = p - py * cw;
-                    const int sc = s_score[(py + 3) * FAST_TP + ox + px + 3];
+                    const int p = i * 32 + bit;
+                    const int py = (int)(((uint32_t)p * invcw) >> 24), px = p - py * cw;
+                    const int sc = s_score[(py + 3) * FAST_TP + cx0 + px];
                     out[k++] = (uint32_t)(px + 3 + cell.xoff) | ((uint32_t)(py + 3 + cell.yoff) << 12) | ((uint32_t)sc << 24);
                 }
             }
@@ -307,10 +423,10 @@ __global__ void __launch_bounds__(FAST_NT) k_fast_cells(const __grid_constant__ 
             return;
         }
         /* empty at iniTh: wipe the scores written so far and retry with minTh (src/ORBextractor.cc:825-828) */
-        for (int e = threadIdx.x; e < nl; e += FAST_NT) {
-            const int p = s_list[e];
-            const int py = p / cw, px = p - py * cw;
-            s_score[(py + 3) * FAST_TP + ox + px + 3] = 0;
+        for (int e = threadIdx.x; e < n2; e += FAST_NT) {
+            const int p = s_list2[e];
+            const int py = (int)(((uint32_t)p * invcw) >> 24), px = p - py * cw;
+            s_score[(py + 3) * FAST_TP + cx0 + px] = 0;
         }
         th = d.minTh;
         __syncthreads();
@@ -738,15 +854,16 @@ __global__ void __launch_bounds__(OD_NT) k_orient_describe(const __grid_constant
     const int u = lane - 15;
     if (lane < 31) {
         const int au = u < 0 ? -u : u;
-#pragma unroll 1
-        for (int v = -15; v <= 15; v++) {
+        int rowsum[31];
+#pragma unroll
+        for (int v = -15; v <= 15; v++) {            /* 31 independent loads in flight */
             const int av = v < 0 ? -v : v;
-            if (au <= c_umax[av]) {
-                const int val = c[v * L.pitch + u];
-                m10 += u * val;
-                m01 += v * val;
-            }
+            rowsum[v + 15] = (au <= c_umax[av]) ? (int)c[v * L.pitch + u] : 0;
         }
+        int colsum = 0;
+#pragma unroll
+        for (int v = -15; v <= 15; v++) { colsum += rowsum[v + 15]; m01 += v * rowsum[v + 15]; }
+        m10 = u * colsum;
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
@@ -759,7 +876,9 @@ __global__ void __launch_bounds__(OD_NT) k_orient_describe(const __grid_constant
      * correctly-rounded value (double evaluation rounded once); see DESIGN.md "float reproducibility". */
     const float factorPI = (float)(3.14159265358979323846 / 180.0);
     const float ang = __fmul_rn(angle, factorPI);
-    const float ca = (float)cos((double)ang), sa = (float)sin((double)ang);
+    double sd, cd;
+    sincos((double)ang, &sd, &cd);
+    const float ca = (float)cd, sa = (float)sd;
     const uint8_t* cb = b.blur + f * d.blurSlab + L.blurOff + (size_t)y * L.bpitch + x;
     const int8_t* p = s_pat + 32 * lane;
     uint32_t val = 0;
@@ -791,8 +910,9 @@ int orbfe_quadtree_smem_bytes(int cap) {
 
 int orbfe_collect_stage_times(orbfe_extractor* ex);
 
-int orbfe_configure_kernels(int quadSmem) {
+int orbfe_configure_kernels(int quadSmem, int fastSmem) {
     ORBFE_CUDA(cudaFuncSetAttribute(k_quadtree, cudaFuncAttributeMaxDynamicSharedMemorySize, quadSmem));
+    ORBFE_CUDA(cudaFuncSetAttribute(k_fast_cells, cudaFuncAttributeMaxDynamicSharedMemorySize, fastSmem));
     return 0;
 }
 
@@ -804,13 +924,18 @@ int orbfe_launch_extract(orbfe_extractor* ex, const uint8_t* d_images, int nfram
 #define STAGE_MARK() do { if (prof) ORBFE_CUDA(cudaEventRecord(ex->ev[e++], st)); } while (0)
     if (prof && ex->stagePending) { int rc = orbfe_collect_stage_times(ex); if (rc) return rc; }
     STAGE_MARK();
-    for (int l = 0; l < d.nlevels; l++) {
-        const LevelDesc& L = d.lv[l];
+    {
+        const LevelDesc& L = d.lv[0];
         const int items = (L.pitch >> 4) * (L.h + 2 * ORBFE_EDGE);
-        k_pyramid_level<<<dim3((items + 255) / 256, nframes), 256, 0, st>>>(d, ex->b, d_images, l);
+        k_pyramid_copy0<<<dim3((items + 255) / 256, nframes), 256, 0, st>>>(d, ex->b, d_images);
+    }
+    for (int l = 1; l < d.nlevels; l++) {
+        const LevelDesc& L = d.lv[l];
+        const int items = (L.pitch >> 2) * (L.h + 2 * ORBFE_EDGE);
+        k_pyramid_level<<<dim3((items + 255) / 256, nframes), 256, 0, st>>>(d, ex->b, l);
     }
     STAGE_MARK();
-    k_fast_cells<<<dim3(d.nCells, nframes), FAST_NT, 0, st>>>(d, ex->b);
+    k_fast_cells<<<dim3(d.nCells, nframes), FAST_NT, ex->fastSmem, st>>>(d, ex->b);
     STAGE_MARK();
     for (int l = 0; l < d.nlevels; l++) {
         const LevelDesc& L = d.lv[l];

@@ -13,7 +13,7 @@
 
 int orbfe_upload_constants(const int* umax16, const int8_t* pattern1024);
 int orbfe_quadtree_smem_bytes(int cap);
-int orbfe_configure_kernels(int quadSmem);
+int orbfe_configure_kernels(int quadSmem, int fastSmem);
 int orbfe_launch_extract(orbfe_extractor* ex, const uint8_t* d_images, int nframes, int lap0, int lap1, cudaStream_t st);
 int orbfe_collect_stage_times(orbfe_extractor* ex);
 
@@ -91,7 +91,7 @@ int orbfe_extractor_create(const orbfe_params* p, int device, int width, int hei
     if (!p || !out) { orbfe_set_error("null argument"); return ORBFE_E_INVALID; }
     *out = nullptr;
     if (p->nlevels < 1 || p->nlevels > ORBFE_MAX_LEVELS || p->nfeatures < 1 || !(p->scale_factor > 1.0f) || max_batch < 1 ||
-        p->ini_th_fast < 1 || p->min_th_fast < 1 || p->ini_th_fast > 254 || p->min_th_fast > 254) {
+        p->ini_th_fast < 1 || p->min_th_fast < 1 || p->ini_th_fast > 127 || p->min_th_fast > 127) {
         orbfe_set_error("unsupported extractor parameters");
         return ORBFE_E_INVALID;
     }
@@ -221,6 +221,7 @@ int orbfe_extractor_create(const orbfe_params* p, int device, int width, int hei
         L.keyCap = keyTotal - L.keyBase;
         nodeCap = std::max(nodeCap, std::max(L.selCap, std::max(L.nIni, L.nCols * L.nRows)));
         if (l > 0) {
+            while (tabs.size() % 4) tabs.push_back(make_uint2(0, 0)); /* k_pyramid_level reads tabX four entries at a time */
             L.tabX = (int)tabs.size();
             linear_table(d.lv[l - 1].w, L.w, tabs);
             L.tabY = (int)tabs.size();
@@ -241,6 +242,16 @@ int orbfe_extractor_create(const orbfe_params* p, int device, int width, int hei
     d.pyrSlab = align_up(pyrOff + 256, 256);
     d.blurSlab = align_up(blurOff + 256, 256);
     ex->quadSmem = orbfe_quadtree_smem_bytes(cap2);
+    {
+        int rows = 8, pix = 8;
+        for (const CellDesc& c : cells) {
+            rows = std::max(rows, (int)c.rh);
+            pix = std::max(pix, std::max(c.rw - 6, 0) * std::max(c.rh - 6, 0));
+        }
+        d.fastRows = rows;
+        d.fastPix = (pix + 7) / 8 * 8;
+        ex->fastSmem = 2 * rows * 80 + 2 * d.fastPix * 2 + ((d.fastPix + 31) / 32 + 1) * 4 + 16;
+    }
 
     int rc = 0;
     const size_t B = (size_t)max_batch;
@@ -284,7 +295,7 @@ int orbfe_extractor_create(const orbfe_params* p, int device, int width, int hei
     TRYC(cudaMallocHost((void**)&ex->hCount, B * sizeof(int)));
     TRYC(cudaMallocHost((void**)&ex->hMono, B * sizeof(int)));
     TRY(orbfe_upload_constants(ex->umax.data(), kPattern));
-    TRY(orbfe_configure_kernels(ex->quadSmem));
+    TRY(orbfe_configure_kernels(ex->quadSmem, ex->fastSmem));
 #undef TRY
 #undef TRYC
     *out = ex;

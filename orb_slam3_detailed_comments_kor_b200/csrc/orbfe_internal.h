@@ -43,6 +43,8 @@ struct ExDesc {
     int kpCap;        /* selected keypoints per frame, all levels (= sum selCap) */
     int nodeCap;      /* quadtree node capacity (max over levels of selCap, padded) */
     int iniTh, minTh;
+    int fastRows;     /* tallest FAST cell ROI (rows of the smem tile) */
+    int fastPix;      /* most candidate pixels in one cell, rounded up to a multiple of 8 */
     size_t pyrSlab;   /* bytes per frame */
     size_t blurSlab;
     LevelDesc lv[ORBFE_MAX_LEVELS];

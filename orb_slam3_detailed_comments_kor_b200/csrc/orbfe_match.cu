@@ -171,105 +171,119 @@ static int launch_top2(const uint8_t* dQ, int nq, const uint8_t* dDb, long long 
 
 /* --------------------------------------------------------------------------------------------------- stereo */
 #define ST_NT 256
-static __device__ __forceinline__ int ham_rows(const uint4* a, const uint4* b) {
-    const uint4 a0 = a[0], a1 = a[1], b0 = b[0], b1 = b[1];
-    return __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) +
-           __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
-}
-
-/* One warp = one left keypoint.  Lanes stride over the right keypoints in index order (the reference's row
- * table lists them in index order too, src/Frame.cc:814-824), keep (distance, index) minima, then the warp
- * does the 11-shift SAD and the parabola fit.  Float steps use round-to-nearest intrinsics (no contraction). */
+#define ST_KPB 32   /* left keypoints per CTA */
+/* One CTA = 32 left keypoints of one frame, one warp = one left keypoint at a time.  The CTA first builds a compact
+ * table of the frame's right keypoints in shared memory (x, row band [floor(y-r), ceil(y+r)], octave; r = 2*scale,
+ * src/Frame.cc:814-824); lanes then stride over that table in index order (the reference's row lists are in index
+ * order too), keep (distance, index) minima, and the warp does the 11-shift SAD and the parabola fit.  Float steps use
+ * round-to-nearest intrinsics (no contraction). */
 __global__ void __launch_bounds__(ST_NT) k_stereo_match(const __grid_constant__ ExDesc d, ExBuffers L, ExBuffers R, float mbf,
                                                         float minD, float maxD) {
+    extern __shared__ __align__(8) uint2 s_right[]; /* (x bits, minr | maxr<<12 | octave<<24) */
     const size_t f = blockIdx.y;
-    const int lane = threadIdx.x & 31;
-    const int iL = blockIdx.x * (ST_NT / 32) + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int n = L.count[f], nR = R.count[f];
-    if (iL >= n) return;
-    const size_t o = f * d.kpCap + iL;
-    float outU = -1.f, outD = -1.f;
-    int outS = -1;
-    const orbfe_keypoint kpL = L.kps[o];
-    const int levelL = kpL.octave;
-    const float vL = kpL.y, uL = kpL.x;
-    const int row = (int)vL;
-    const float minU = __fsub_rn(uL, maxD), maxU = __fsub_rn(uL, minD);
-    int best = 100, bestR = 0x7FFFFFFF; /* TH_HIGH, src/ORBmatcher.cc:36 */
-    if (!(maxU < 0)) {
-        const uint4* dL = reinterpret_cast<const uint4*>(L.desc + o * 32);
+    if ((int)blockIdx.x * ST_KPB >= n) return;
+    {
         const orbfe_keypoint* kR = R.kps + f * d.kpCap;
-        for (int iR = lane; iR < nR; iR += 32) {
-            const orbfe_keypoint k = kR[iR];
+        for (int i = threadIdx.x; i < nR; i += ST_NT) {
+            const orbfe_keypoint k = kR[i];
             const float r = __fmul_rn(2.0f, d.lv[k.octave].scale);
-            const int maxr = (int)ceilf(__fadd_rn(k.y, r)), minr = (int)floorf(__fsub_rn(k.y, r));
-            if (row < minr || row > maxr) continue;
-            if (k.octave < levelL - 1 || k.octave > levelL + 1) continue;
-            if (k.x >= minU && k.x <= maxU) {
-                const int dist = ham_rows(dL, reinterpret_cast<const uint4*>(R.desc + (f * d.kpCap + iR) * 32));
-                if (dist < best) { best = dist; bestR = iR; }
-            }
-        }
-#pragma unroll
-        for (int s = 16; s > 0; s >>= 1) {
-            const int ob = __shfl_xor_sync(0xFFFFFFFFu, best, s), oi = __shfl_xor_sync(0xFFFFFFFFu, bestR, s);
-            if (ob < best || (ob == best && oi < bestR)) { best = ob; bestR = oi; }
+            const int maxr = max(0, min(4095, (int)ceilf(__fadd_rn(k.y, r)))), minr = max(0, min(4095, (int)floorf(__fsub_rn(k.y, r))));
+            s_right[i] = make_uint2(__float_as_uint(k.x), (uint32_t)minr | ((uint32_t)maxr << 12) | ((uint32_t)k.octave << 24));
         }
     }
-    if (best < 75 && !(maxU < 0)) { /* thOrbDist = (TH_HIGH+TH_LOW)/2, src/Frame.cc:802 */
-        const LevelDesc& lv = d.lv[levelL];
-        const float uR0 = R.kps[f * d.kpCap + bestR].x;
-        const float sf = __fdiv_rn(1.0f, lv.scale); /* mvInvScaleFactors[octave] */
-        const float suL = roundf(__fmul_rn(kpL.x, sf)), svL = roundf(__fmul_rn(kpL.y, sf)), suR0 = roundf(__fmul_rn(uR0, sf));
-        const float iniu = __fsub_rn(__fadd_rn(suR0, 5.f), 5.f), endu = __fadd_rn(__fadd_rn(__fadd_rn(suR0, 5.f), 5.f), 1.f);
-        if (!(iniu < 0 || endu >= (float)lv.w)) {
-            const int y0 = (int)__fsub_rn(svL, 5.f), xl0 = (int)__fsub_rn(suL, 5.f), xr0 = (int)suR0 - 5;
-            const uint8_t* pl = L.pyr + f * d.pyrSlab + lv.pyrOff + (size_t)(y0 + ORBFE_EDGE) * lv.pitch + ORBFE_ROW_LEAD + xl0;
-            const uint8_t* pr = R.pyr + f * d.pyrSlab + lv.pyrOff + (size_t)(y0 + ORBFE_EDGE) * lv.pitch + ORBFE_ROW_LEAD + xr0;
-            int sad[11];
-#pragma unroll
-            for (int k = 0; k < 11; k++) sad[k] = 0;
-            for (int p = lane; p < 121; p += 32) {
-                const int dy = p / 11, dx = p - dy * 11;
-                const int a = pl[dy * lv.pitch + dx];
-                const uint8_t* rr = pr + dy * lv.pitch + dx - 5;
-#pragma unroll
-                for (int k = 0; k < 11; k++) sad[k] += abs(a - (int)rr[k]);
+    __syncthreads();
+    for (int it = warp; it < ST_KPB; it += ST_NT / 32) {
+        const int iL = blockIdx.x * ST_KPB + it;
+        if (iL >= n) break;
+        const size_t o = f * d.kpCap + iL;
+        float outU = -1.f, outD = -1.f;
+        int outS = -1;
+        const orbfe_keypoint kpL = L.kps[o];
+        const int levelL = kpL.octave;
+        const float vL = kpL.y, uL = kpL.x;
+        const int row = (int)vL;
+        const float minU = __fsub_rn(uL, maxD), maxU = __fsub_rn(uL, minD);
+        int best = 100, bestR = 0x7FFFFFFF; /* TH_HIGH, src/ORBmatcher.cc:36 */
+        if (!(maxU < 0)) {
+            const uint4* dL = reinterpret_cast<const uint4*>(L.desc + o * 32);
+            const uint4 dl0 = dL[0], dl1 = dL[1];
+            for (int iR = lane; iR < nR; iR += 32) {
+                const uint2 k = s_right[iR];
+                const int minr = k.y & 0xFFF, maxr = (k.y >> 12) & 0xFFF, oct = k.y >> 24;
+                if (row < minr || row > maxr) continue;
+                if (oct < levelL - 1 || oct > levelL + 1) continue;
+                const float uR = __uint_as_float(k.x);
+                if (uR >= minU && uR <= maxU) {
+                    const uint4* dR = reinterpret_cast<const uint4*>(R.desc + (f * d.kpCap + iR) * 32);
+                    const uint4 b0 = dR[0], b1 = dR[1];
+                    const int dist = __popc(dl0.x ^ b0.x) + __popc(dl0.y ^ b0.y) + __popc(dl0.z ^ b0.z) + __popc(dl0.w ^ b0.w) +
+                                     __popc(dl1.x ^ b1.x) + __popc(dl1.y ^ b1.y) + __popc(dl1.z ^ b1.z) + __popc(dl1.w ^ b1.w);
+                    if (dist < best) { best = dist; bestR = iR; }
+                }
             }
 #pragma unroll
-            for (int k = 0; k < 11; k++)
+            for (int s = 16; s > 0; s >>= 1) {
+                const int ob = __shfl_xor_sync(0xFFFFFFFFu, best, s), oi = __shfl_xor_sync(0xFFFFFFFFu, bestR, s);
+                if (ob < best || (ob == best && oi < bestR)) { best = ob; bestR = oi; }
+            }
+        }
+        if (best < 75 && !(maxU < 0)) { /* thOrbDist = (TH_HIGH+TH_LOW)/2, src/Frame.cc:802 */
+            const LevelDesc& lv = d.lv[levelL];
+            const float uR0 = __uint_as_float(s_right[bestR].x);
+            const float sf = __fdiv_rn(1.0f, lv.scale); /* mvInvScaleFactors[octave] */
+            const float suL = roundf(__fmul_rn(kpL.x, sf)), svL = roundf(__fmul_rn(kpL.y, sf)), suR0 = roundf(__fmul_rn(uR0, sf));
+            const float iniu = __fsub_rn(__fadd_rn(suR0, 5.f), 5.f), endu = __fadd_rn(__fadd_rn(__fadd_rn(suR0, 5.f), 5.f), 1.f);
+            if (!(iniu < 0 || endu >= (float)lv.w)) {
+                const int y0 = (int)__fsub_rn(svL, 5.f), xl0 = (int)__fsub_rn(suL, 5.f), xr0 = (int)suR0 - 5;
+                const uint8_t* pl = L.pyr + f * d.pyrSlab + lv.pyrOff + (size_t)(y0 + ORBFE_EDGE) * lv.pitch + ORBFE_ROW_LEAD + xl0;
+                const uint8_t* pr = R.pyr + f * d.pyrSlab + lv.pyrOff + (size_t)(y0 + ORBFE_EDGE) * lv.pitch + ORBFE_ROW_LEAD + xr0;
+                int sad[11];
 #pragma unroll
-                for (int s = 16; s > 0; s >>= 1) sad[k] += __shfl_xor_sync(0xFFFFFFFFu, sad[k], s);
-            int bestS = 0x7FFFFFFF, bestInc = 0;
+                for (int k = 0; k < 11; k++) sad[k] = 0;
+                for (int p = lane; p < 121; p += 32) {
+                    const int dy = p / 11, dx = p - dy * 11;
+                    const int a = pl[dy * lv.pitch + dx];
+                    const uint8_t* rr = pr + dy * lv.pitch + dx - 5;
 #pragma unroll
-            for (int k = 0; k < 11; k++)
-                if (sad[k] < bestS) { bestS = sad[k]; bestInc = k - 5; }
-            if (bestInc != -5 && bestInc != 5) {
-                float d1 = 0.f, d2 = 0.f, d3 = 0.f;
+                    for (int k = 0; k < 11; k++) sad[k] += abs(a - (int)rr[k]);
+                }
 #pragma unroll
-                for (int k = 1; k < 10; k++)
-                    if (k == bestInc + 5) { d1 = (float)sad[k - 1]; d2 = (float)sad[k]; d3 = (float)sad[k + 1]; }
-                const float deltaR = __fdiv_rn(__fsub_rn(d1, d3), __fmul_rn(2.0f, __fsub_rn(__fadd_rn(d1, d3), __fmul_rn(2.0f, d2))));
-                if (!(deltaR < -1 || deltaR > 1)) {
-                    float bestuR = __fmul_rn(lv.scale, __fadd_rn(__fadd_rn(suR0, (float)bestInc), deltaR));
-                    float disparity = __fsub_rn(uL, bestuR);
-                    if (disparity >= minD && disparity < maxD) {
-                        if (disparity <= 0) {
-                            disparity = 0.01f;
-                            bestuR = (float)((double)uL - 0.01);
+                for (int k = 0; k < 11; k++)
+#pragma unroll
+                    for (int s = 16; s > 0; s >>= 1) sad[k] += __shfl_xor_sync(0xFFFFFFFFu, sad[k], s);
+                int bestS = 0x7FFFFFFF, bestInc = 0;
+#pragma unroll
+                for (int k = 0; k < 11; k++)
+                    if (sad[k] < bestS) { bestS = sad[k]; bestInc = k - 5; }
+                if (bestInc != -5 && bestInc != 5) {
+                    float d1 = 0.f, d2 = 0.f, d3 = 0.f;
+#pragma unroll
+                    for (int k = 1; k < 10; k++)
+                        if (k == bestInc + 5) { d1 = (float)sad[k - 1]; d2 = (float)sad[k]; d3 = (float)sad[k + 1]; }
+                    const float deltaR = __fdiv_rn(__fsub_rn(d1, d3), __fmul_rn(2.0f, __fsub_rn(__fadd_rn(d1, d3), __fmul_rn(2.0f, d2))));
+                    if (!(deltaR < -1 || deltaR > 1)) {
+                        float bestuR = __fmul_rn(lv.scale, __fadd_rn(__fadd_rn(suR0, (float)bestInc), deltaR));
+                        float disparity = __fsub_rn(uL, bestuR);
+                        if (disparity >= minD && disparity < maxD) {
+                            if (disparity <= 0) {
+                                disparity = 0.01f;
+                                bestuR = (float)((double)uL - 0.01);
+                            }
+                            outD = __fdiv_rn(mbf, disparity);
+                            outU = bestuR;
+                            outS = bestS;
                         }
-                        outD = __fdiv_rn(mbf, disparity);
-                        outU = bestuR;
-                        outS = bestS;
                     }
                 }
             }
         }
-    }
-    if (lane == 0) {
-        L.uRight[o] = outU;
-        L.depth[o] = outD;
-        L.sadBest[o] = outS;
+        if (lane == 0) {
+            L.uRight[o] = outU;
+            L.depth[o] = outD;
+            L.sadBest[o] = outS;
+        }
     }
 }
 
@@ -341,11 +355,13 @@ int orbfe_stereo_match_batch_device(orbfe_extractor* exL, orbfe_extractor* exR, 
     ORBFE_CUDA(cudaSetDevice(exL->device));
     cudaStream_t st = stream ? (cudaStream_t)stream : exL->stream;
     if (!stream) ORBFE_CUDA(cudaStreamSynchronize(exR->stream)); /* right extraction ran on its own stream */
+    const size_t stSmem = (size_t)exL->d.kpCap * sizeof(uint2);
+    if (stSmem > 48 * 1024) ORBFE_CUDA(cudaFuncSetAttribute(k_stereo_match, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)stSmem));
     const bool prof = exL->profiling != 0;
     if (prof && exL->stereoPending) { int rc = orbfe_collect_stage_times(exL); if (rc) return rc; }
     cudaEvent_t* ev = exL->ev + ORBFE_NUM_STAGES + 1; /* two private events: the extractor's own stay untouched */
     if (prof) ORBFE_CUDA(cudaEventRecord(ev[0], st));
-    k_stereo_match<<<dim3((exL->d.kpCap + ST_NT / 32 - 1) / (ST_NT / 32), nframes), ST_NT, 0, st>>>(exL->d, exL->b, exR->b, mbf, minD, maxD);
+    k_stereo_match<<<dim3((exL->d.kpCap + ST_KPB - 1) / ST_KPB, nframes), ST_NT, stSmem, st>>>(exL->d, exL->b, exR->b, mbf, minD, maxD);
     k_stereo_median<<<nframes, 256, 0, st>>>(exL->d, exL->b);
     exL->launches += 2;
     ORBFE_CUDA(cudaGetLastError());
