@@ -18,7 +18,8 @@
 #include "orbfe_internal.h"
 
 __constant__ int c_umax[16];
-__constant__ __align__(16) int8_t c_pattern[1024];
+__device__ __align__(16) float g_patternf[1024];   /* bit_pattern_31_ as floats: (x0,y0,x1,y1) per test */
+__constant__ uint32_t c_rowmask[32];               /* lane u-15: bit v+15 set iff |u| <= umax[|v|] */
 
 static __device__ __forceinline__ int reflect101(int p, int n) {
     /* |overshoot| <= 19 < n: one reflection is enough (cv::copyMakeBorder BORDER_REFLECT_101) */
@@ -72,25 +73,39 @@ static __device__ __forceinline__ uint32_t resize_px_generic(const uint8_t* r0, 
 }
 
 __global__ void __launch_bounds__(256) k_pyramid_level(const __grid_constant__ ExDesc d, ExBuffers b, int level) {
+    /* block = 32 x 8: a warp works on one output row.  Warps [0, nInteriorWarps) take the groups that lie fully inside
+     * the image (fast path, no divergence); the last warp of the row takes every group that touches the border. */
     const LevelDesc& L = d.lv[level];
     const LevelDesc& P = d.lv[level - 1];
+    const int row = blockIdx.y * 8 + threadIdx.y;
+    if (row >= L.h + 2 * ORBFE_EDGE) return;
     const int groups = L.pitch >> 2;
-    const int rows = L.h + 2 * ORBFE_EDGE;
-    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= groups * rows) return;
-    const int row = idx / groups, g = idx - row * groups;
-    const size_t f = blockIdx.y;
+    const int gFirst = ORBFE_ROW_LEAD / 4, nInt = L.w >> 2;     /* interior groups: px0 = 0, 4, ... */
+    const int tx = blockIdx.x * 32 + threadIdx.x;
+    const int intThreads = (nInt + 31) & ~31;
+    int g;
+    bool interior;
+    if (tx < intThreads) {
+        if (tx >= nInt) return;
+        g = gFirst + tx;
+        interior = true;
+    } else {
+        const int j = tx - intThreads;                          /* border groups: [0, gFirst) then [gFirst+nInt, groups) */
+        g = j < gFirst ? j : gFirst + nInt + (j - gFirst);
+        if (g >= groups) return;
+        interior = false;
+    }
+    const size_t f = blockIdx.z;
     uint8_t* slab = b.pyr + f * d.pyrSlab;
     const int yi = reflect101(row - ORBFE_EDGE, L.h);
-    const uint8_t* sint = slab + P.pyrOff + (size_t)ORBFE_EDGE * P.pitch + ORBFE_ROW_LEAD;
     const uint2 yt = __ldg(b.tabs + L.tabY + yi);
     /* row yt.x+1 and column sx+1 may be the source's own border: their coefficient is then 0 */
-    const uint8_t* r0 = sint + (size_t)yt.x * P.pitch;
+    const uint8_t* r0 = slab + (uint32_t)(P.pyrOff + (ORBFE_EDGE + (int)yt.x) * P.pitch + ORBFE_ROW_LEAD);
     const uint8_t* r1 = r0 + P.pitch;
     const int b0 = yt.y & 0xFFFF, b1 = yt.y >> 16;
     const int px0 = g * 4 - ORBFE_ROW_LEAD;
     uint32_t out = 0;
-    if (px0 >= 0 && px0 + 4 <= L.w) {
+    if (interior) {
         const uint4* tp = reinterpret_cast<const uint4*>(b.tabs + L.tabX + px0); /* tabX is 4-entry aligned */
         const uint4 ta = __ldg(tp), tb = __ldg(tp + 1); /* entries (sx, c0|c1<<16) of the four pixels */
         const uint32_t sx0 = ta.x;
@@ -104,7 +119,7 @@ __global__ void __launch_bounds__(256) k_pyramid_level(const __grid_constant__ E
         const uint32_t cfs[4] = {ta.y, ta.w, tb.y, tb.w};
 #pragma unroll
         for (int k = 0; k < 4; k++) {
-            const uint32_t off = sxs[k] - sx0;            /* 0..4: 1.2x downscale keeps four taps within 6 bytes */
+            const uint32_t off = sxs[k] - sx0;            /* 0..6 (host-checked): four taps within 8 bytes */
             const uint32_t sel = off * 0x11u + 0x10u;     /* bytes (off, off+1) -> low half */
             const uint32_t h0 = __dp2a_lo(cfs[k], __byte_perm(u0, u1, sel), 0u);
             const uint32_t h1 = __dp2a_lo(cfs[k], __byte_perm(v0, v1, sel), 0u);
@@ -119,7 +134,7 @@ __global__ void __launch_bounds__(256) k_pyramid_level(const __grid_constant__ E
                 out |= resize_px_generic(r0, r1, __ldg(b.tabs + L.tabX + reflect101(px, L.w)), b0, b1) << (8 * k);
         }
     }
-    *reinterpret_cast<uint32_t*>(slab + L.pyrOff + (size_t)row * L.pitch + g * 4) = out;
+    *reinterpret_cast<uint32_t*>(slab + (uint32_t)(L.pyrOff + row * L.pitch + g * 4)) = out;
 }
 
 /* --------------------------------------------------------------------------------------------------- blur */
@@ -129,24 +144,26 @@ __global__ void __launch_bounds__(256) k_pyramid_level(const __grid_constant__ E
  * are stored as vertically adjacent 16-bit pairs (rows 2j, 2j+1 of the tile in one 32-bit word), so the vertical
  * pass is four DP2A (16-bit x 8-bit pairs) per pixel and one thread produces a 4 x 2 block from five 128-bit loads. */
 #define BLUR_TW 64
-#define BLUR_TH 32
+#define BLUR_TH 56
 #define BLUR_PAIRS (BLUR_TH / 2 + 4)   /* tile rows y0-4 .. y0+TH+3 as pairs */
 __global__ void __launch_bounds__(256) k_blur7(const __grid_constant__ ExDesc d, ExBuffers b, int level) {
     __shared__ __align__(16) uint32_t s_h[BLUR_PAIRS][BLUR_TW];
     const LevelDesc& L = d.lv[level];
     const size_t f = blockIdx.z;
     const int x0 = blockIdx.x * BLUR_TW, y0 = blockIdx.y * BLUR_TH;
-    const uint8_t* pad = b.pyr + f * d.pyrSlab + L.pyrOff;
+    const uint8_t* pad = b.pyr + f * d.pyrSlab + L.pyrOff + ORBFE_ROW_LEAD + x0 - 4;
     const uint32_t KLO = 18u | (34u << 8) | (48u << 16) | (56u << 24);  /* taps -3..0 */
     const uint32_t KHI = 48u | (34u << 8) | (18u << 16);                /* taps +1..+3 */
     const int ymax = L.h + ORBFE_EDGE - 1;
-    for (int i = threadIdx.x; i < BLUR_PAIRS * (BLUR_TW / 4); i += 256) {
-        const int j = i >> 4, q = i & 15;                 /* row pair j, pixel group q (4 px) */
+    static_assert(BLUR_PAIRS * (BLUR_TW / 4) % 256 == 0 && BLUR_TW == 64, "horizontal pass assumes whole sweeps of 256 threads");
+#pragma unroll
+    for (int sweep = 0; sweep < BLUR_PAIRS * (BLUR_TW / 4) / 256; sweep++) {
+        const int j = (threadIdx.x >> 4) + 16 * sweep, q = threadIdx.x & 15; /* row pair j, pixel group q (4 px) */
         uint32_t hrow[2][4];
 #pragma unroll
         for (int rr = 0; rr < 2; rr++) {
             const int gy = min(y0 - 4 + 2 * j + rr, ymax);
-            const uint32_t* p = reinterpret_cast<const uint32_t*>(pad + (size_t)(gy + ORBFE_EDGE) * L.pitch + ORBFE_ROW_LEAD + x0 + 4 * q - 4);
+            const uint32_t* p = reinterpret_cast<const uint32_t*>(pad + (uint32_t)((gy + ORBFE_EDGE) * L.pitch + 4 * q));
             const uint32_t w0 = __ldg(p), w1 = __ldg(p + 1), w2 = __ldg(p + 2);   /* px x-4..x-1 | x..x+3 | x+4..x+7 */
             hrow[rr][0] = __dp4a(__funnelshift_r(w0, w1, 8), KLO, __dp4a(__funnelshift_r(w1, w2, 8), KHI, 0u));
             hrow[rr][1] = __dp4a(__funnelshift_r(w0, w1, 16), KLO, __dp4a(__funnelshift_r(w1, w2, 16), KHI, 0u));
@@ -159,9 +176,11 @@ __global__ void __launch_bounds__(256) k_blur7(const __grid_constant__ ExDesc d,
     __syncthreads();
     uint8_t* dst = b.blur + f * d.blurSlab + L.blurOff;
     /* one item = output rows (y0+2m, y0+2m+1) x 4 pixels; needs pairs m .. m+4 (rows y0+2m-4 .. y0+2m+5) */
-    const int m = threadIdx.x >> 4, q = threadIdx.x & 15;
+#pragma unroll
+    for (int sweep = 0; sweep < (BLUR_TH / 2 + 15) / 16; sweep++) {
+    const int m = (threadIdx.x >> 4) + 16 * sweep, q = threadIdx.x & 15;
     const int gy = y0 + 2 * m, gx = x0 + 4 * q;
-    if (gy < L.h && gx < L.bpitch) {
+    if (m < BLUR_TH / 2 && gy < L.h && gx < L.bpitch) {
         uint4 pr[5];
 #pragma unroll
         for (int k = 0; k < 5; k++) pr[k] = *reinterpret_cast<const uint4*>(&s_h[m + k][4 * q]);
@@ -178,8 +197,10 @@ __global__ void __launch_bounds__(256) k_blur7(const __grid_constant__ ExDesc d,
             oe |= (ve >> 16) << (8 * k);
             oo |= (vo >> 16) << (8 * k);
         }
-        *reinterpret_cast<uint32_t*>(dst + (size_t)gy * L.bpitch + gx) = oe;
-        if (gy + 1 < L.h) *reinterpret_cast<uint32_t*>(dst + (size_t)(gy + 1) * L.bpitch + gx) = oo;
+        uint8_t* o = dst + (uint32_t)(gy * L.bpitch + gx);
+        *reinterpret_cast<uint32_t*>(o) = oe;
+        if (gy + 1 < L.h) *reinterpret_cast<uint32_t*>(o + L.bpitch) = oo;
+    }
     }
 }
 
@@ -203,7 +224,9 @@ static __host__ __device__ __forceinline__ bool run9(uint32_t m) {
     return (x & 0xFFFFu) != 0;
 }
 
-/* corner at threshold t  <=>  9 contiguous ring pixels all > v+t or all < v-t */
+/* corner at threshold t  <=>  9 contiguous ring pixels all > v+t or all < v-t.
+ * Masks are gathered with one funnel shift per ring pixel: (B << 1) | sign(v + t - p) collects "p > v+t" (the bit
+ * order comes out reversed, which a circular run test does not care about). */
 static __host__ __device__ __forceinline__ bool fast_is_corner(const uint8_t* c, int t) {
     const int v = c[0];
     const int hi = v + t, lo = v - t;
@@ -217,8 +240,13 @@ static __host__ __device__ __forceinline__ bool fast_is_corner(const uint8_t* c,
 #pragma unroll
     for (int k = 0; k < 16; k++) {
         const int p = c[RING_OFF(k, FAST_TP)];
-        B |= (uint32_t)(p > hi) << k;
-        D |= (uint32_t)(p < lo) << k;
+#ifdef __CUDA_ARCH__
+        B = __funnelshift_l((uint32_t)(hi - p), B, 1);   /* sign bit set <=> p > hi */
+        D = __funnelshift_l((uint32_t)(p - lo), D, 1);   /* sign bit set <=> p < lo */
+#else
+        B = (B << 1) | ((uint32_t)(hi - p) >> 31);
+        D = (D << 1) | ((uint32_t)(p - lo) >> 31);
+#endif
     }
     return run9(B) || run9(D);
 }
@@ -289,21 +317,24 @@ __global__ void __launch_bounds__(FAST_NT, 8) k_fast_cells(const __grid_constant
     const LevelDesc& L = d.lv[cell.level];
     const int ox = cell.x0 & 3;
     {
-        const uint8_t* g = b.pyr + f * d.pyrSlab + L.pyrOff + (size_t)(cell.y0 + ORBFE_EDGE) * L.pitch + ORBFE_ROW_LEAD + (cell.x0 - ox);
-        const int nw = (ox + cell.rw + 3) >> 2;
-        for (int i = threadIdx.x; i < cell.rh * nw; i += FAST_NT) {
-            const int r = i / nw, c = i - r * nw;
-            reinterpret_cast<uint32_t*>(s_img + r * FAST_TP)[c] = __ldg(reinterpret_cast<const uint32_t*>(g + (size_t)r * L.pitch + 4 * c));
+        /* tile load + score clear: 8 rows x 16 words per sweep, no index arithmetic beyond adds */
+        const int tr = threadIdx.x >> 4, tc = threadIdx.x & 15;
+        const int pitch = L.pitch, nw = cell.nw;
+        const uint8_t* g = b.pyr + f * d.pyrSlab + L.pyrOff + (size_t)(cell.y0 + ORBFE_EDGE + tr) * pitch + ORBFE_ROW_LEAD + (cell.x0 - ox) + 4 * tc;
+        uint32_t* ti = reinterpret_cast<uint32_t*>(s_img) + tr * (FAST_TP / 4) + tc;
+        uint32_t* ts = reinterpret_cast<uint32_t*>(s_score) + tr * (FAST_TP / 4) + tc;
+        for (int r = tr; r < cell.rh; r += FAST_NT / 16, g += (FAST_NT / 16) * pitch, ti += (FAST_NT / 16) * (FAST_TP / 4), ts += (FAST_NT / 16) * (FAST_TP / 4)) {
+            if (tc < nw) { ti[0] = __ldg(reinterpret_cast<const uint32_t*>(g)); ts[0] = 0; }
+            if (tc + 16 < nw) { ti[16] = __ldg(reinterpret_cast<const uint32_t*>(g + 64)); ts[16] = 0; }
         }
-        for (int i = threadIdx.x; i < cell.rh * (FAST_TP / 16); i += FAST_NT) reinterpret_cast<uint4*>(s_score)[i] = make_uint4(0, 0, 0, 0);
     }
     const int npix = cw * ch;
     const int nwords = (npix + 31) >> 5;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const uint32_t invcw = (16777216u + cw - 1) / cw; /* p / cw == (p * invcw) >> 24 for p < 70*70 */
+    const uint32_t invcw = cell.invcw; /* p / cw == (p * invcw) >> 24 for p < 70*70 */
     /* candidate columns are tile columns [cx0, cx0+cw); the sieve walks the tile words that overlap them */
-    const int cx0 = ox + 3, w0 = cx0 >> 2, ngw = ((cx0 + cw - 1) >> 2) - w0 + 1;
-    const uint32_t invgw = (16777216u + ngw - 1) / ngw;
+    const int cx0 = ox + 3, w0 = cx0 >> 2, ngw = cell.ngw;
+    const uint32_t invgw = cell.invgw;
     const int nitems = ch * ngw;
     int th = d.iniTh;
     for (int pass = 0; pass < 2; pass++) {
@@ -324,10 +355,10 @@ __global__ void __launch_bounds__(FAST_NT, 8) k_fast_cells(const __grid_constant
                 const uint32_t top = row[wi + 3 * (FAST_TP / 4)], bot = row[wi - 3 * (FAST_TP / 4)];
                 hit = fast_sieve4(c, top, bot, __byte_perm(lw, c, 0x4321), __byte_perm(c, rw, 0x6543), k127mt);
                 col0 = 4 * wi - cx0; /* candidate x of byte 0 (may be negative at the left edge) */
-                /* drop lanes outside [0, cw) */
-#pragma unroll
-                for (int k = 0; k < 4; k++)
-                    if (col0 + k < 0 || col0 + k >= cw) hit &= ~(0x80u << (8 * k));
+                /* drop the bytes of the first / last word that lie outside the candidate columns */
+                const int gi = wi - w0;
+                if (gi == 0) hit &= cell.edgeL;
+                if (gi == ngw - 1) hit &= cell.edgeR;
             }
             const int cnt = __popc(hit);
             int incl = cnt;
@@ -833,11 +864,12 @@ static __device__ __forceinline__ float fast_atan2_deg(float y, float x) {
 }
 
 #define OD_NT 256
-/* One warp = one keypoint.  IC_Angle: lane u-15 walks the 31 rows of the radius-15 disc on the unblurred level,
- * moments reduced by shuffles.  rBRIEF: lane i builds descriptor byte i from 16 rotated taps of the blurred level. */
+/* One warp = one keypoint.  IC_Angle: lane u-15 walks the 31 rows of the radius-15 disc on the unblurred level
+ * (a per-lane row mask says which rows belong to the disc), moments reduced by shuffles.  rBRIEF: lane i builds
+ * descriptor byte i from 16 rotated taps of the blurred level. */
 __global__ void __launch_bounds__(OD_NT) k_orient_describe(const __grid_constant__ ExDesc d, ExBuffers b) {
-    __shared__ int8_t s_pat[1024];
-    reinterpret_cast<uint32_t*>(s_pat)[threadIdx.x] = reinterpret_cast<const uint32_t*>(c_pattern)[threadIdx.x];
+    __shared__ __align__(16) float s_pat[1024];
+    reinterpret_cast<float4*>(s_pat)[threadIdx.x] = __ldg(reinterpret_cast<const float4*>(g_patternf) + threadIdx.x);
     __syncthreads();
     const size_t f = blockIdx.y;
     const int lane = threadIdx.x & 31;
@@ -848,23 +880,20 @@ __global__ void __launch_bounds__(OD_NT) k_orient_describe(const __grid_constant
     const int l = wk.y & 0xFF, slot = wk.y >> 8;
     const LevelDesc& L = d.lv[l];
 
-    /* IC_Angle, src/ORBextractor.cc:75-102 */
-    const uint8_t* c = b.pyr + f * d.pyrSlab + L.pyrOff + (size_t)(y + ORBFE_EDGE) * L.pitch + ORBFE_ROW_LEAD + x;
-    int m10 = 0, m01 = 0;
+    /* IC_Angle, src/ORBextractor.cc:75-102: m10 = sum u*I, m01 = sum v*I over the disc */
     const int u = lane - 15;
-    if (lane < 31) {
-        const int au = u < 0 ? -u : u;
-        int rowsum[31];
+    const int pitch = L.pitch;
+    const uint8_t* p = b.pyr + f * d.pyrSlab + (uint32_t)(L.pyrOff + (y + ORBFE_EDGE - 15) * pitch + ORBFE_ROW_LEAD + x + u);
+    const uint32_t rows = c_rowmask[lane];
+    int colsum = 0, m01 = 0;
 #pragma unroll
-        for (int v = -15; v <= 15; v++) {            /* 31 independent loads in flight */
-            const int av = v < 0 ? -v : v;
-            rowsum[v + 15] = (au <= c_umax[av]) ? (int)c[v * L.pitch + u] : 0;
-        }
-        int colsum = 0;
-#pragma unroll
-        for (int v = -15; v <= 15; v++) { colsum += rowsum[v + 15]; m01 += v * rowsum[v + 15]; }
-        m10 = u * colsum;
+    for (int v = -15; v <= 15; v++, p += pitch) {
+        int val = 0;
+        if (rows & (1u << (v + 15))) val = *p;
+        colsum += val;
+        m01 += v * val;
     }
+    int m10 = u * colsum;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
         m10 += __shfl_xor_sync(0xFFFFFFFFu, m10, o);
@@ -879,27 +908,45 @@ __global__ void __launch_bounds__(OD_NT) k_orient_describe(const __grid_constant
     double sd, cd;
     sincos((double)ang, &sd, &cd);
     const float ca = (float)cd, sa = (float)sd;
-    const uint8_t* cb = b.blur + f * d.blurSlab + L.blurOff + (size_t)y * L.bpitch + x;
-    const int8_t* p = s_pat + 32 * lane;
-    uint32_t val = 0;
+    const int bpitch = L.bpitch;
+    const uint8_t* cb = b.blur + f * d.blurSlab + (uint32_t)(L.blurOff + y * bpitch + x);
+    const float4* pt = reinterpret_cast<const float4*>(s_pat) + 8 * lane;
+    int off[16];
 #pragma unroll
     for (int k = 0; k < 8; k++) {
-        const float x0 = (float)p[4 * k], y0 = (float)p[4 * k + 1], x1 = (float)p[4 * k + 2], y1 = (float)p[4 * k + 3];
-        const int r0 = __float2int_rn(__fadd_rn(__fmul_rn(x0, sa), __fmul_rn(y0, ca)));
-        const int q0 = __float2int_rn(__fsub_rn(__fmul_rn(x0, ca), __fmul_rn(y0, sa)));
-        const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, sa), __fmul_rn(y1, ca)));
-        const int q1 = __float2int_rn(__fsub_rn(__fmul_rn(x1, ca), __fmul_rn(y1, sa)));
-        const int t0 = cb[r0 * L.bpitch + q0], t1 = cb[r1 * L.bpitch + q1];
-        val |= (uint32_t)(t0 < t1) << k;
+        const float4 t = pt[k]; /* x0, y0, x1, y1 */
+        const int r0 = __float2int_rn(__fadd_rn(__fmul_rn(t.x, sa), __fmul_rn(t.y, ca)));
+        const int q0 = __float2int_rn(__fsub_rn(__fmul_rn(t.x, ca), __fmul_rn(t.y, sa)));
+        const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(t.z, sa), __fmul_rn(t.w, ca)));
+        const int q1 = __float2int_rn(__fsub_rn(__fmul_rn(t.z, ca), __fmul_rn(t.w, sa)));
+        off[2 * k] = r0 * bpitch + q0;
+        off[2 * k + 1] = r1 * bpitch + q1;
     }
+    int tv[16];
+#pragma unroll
+    for (int k = 0; k < 16; k++) tv[k] = cb[off[k]];   /* 16 independent gathers in flight */
+    uint32_t val = 0;
+#pragma unroll
+    for (int k = 0; k < 8; k++) val |= (uint32_t)(tv[2 * k] < tv[2 * k + 1]) << k;
     b.desc[(f * d.kpCap + slot) * 32 + lane] = (uint8_t)val;
     if (lane == 0) b.kps[f * d.kpCap + slot].angle = angle;
 }
 
 /* --------------------------------------------------------------------------------------------- host driver */
 int orbfe_upload_constants(const int* umax16, const int8_t* pattern1024) {
+    float pf[1024];
+    for (int i = 0; i < 1024; i++) pf[i] = (float)pattern1024[i];
+    uint32_t rowmask[32];
+    for (int lane = 0; lane < 32; lane++) {
+        const int u = lane - 15, au = u < 0 ? -u : u;
+        uint32_t m = 0;
+        for (int v = -15; v <= 15; v++)
+            if (lane < 31 && au <= umax16[v < 0 ? -v : v]) m |= 1u << (v + 15);
+        rowmask[lane] = m;
+    }
     ORBFE_CUDA(cudaMemcpyToSymbol(c_umax, umax16, 16 * sizeof(int)));
-    ORBFE_CUDA(cudaMemcpyToSymbol(c_pattern, pattern1024, 1024));
+    ORBFE_CUDA(cudaMemcpyToSymbol(g_patternf, pf, sizeof pf));
+    ORBFE_CUDA(cudaMemcpyToSymbol(c_rowmask, rowmask, sizeof rowmask));
     return 0;
 }
 
@@ -931,8 +978,8 @@ int orbfe_launch_extract(orbfe_extractor* ex, const uint8_t* d_images, int nfram
     }
     for (int l = 1; l < d.nlevels; l++) {
         const LevelDesc& L = d.lv[l];
-        const int items = (L.pitch >> 2) * (L.h + 2 * ORBFE_EDGE);
-        k_pyramid_level<<<dim3((items + 255) / 256, nframes), 256, 0, st>>>(d, ex->b, l);
+        const int nInt = L.w >> 2, intWarps = (nInt + 31) / 32;
+        k_pyramid_level<<<dim3(intWarps + 1, (L.h + 2 * ORBFE_EDGE + 7) / 8, nframes), dim3(32, 8), 0, st>>>(d, ex->b, l);
     }
     STAGE_MARK();
     k_fast_cells<<<dim3(d.nCells, nframes), FAST_NT, ex->fastSmem, st>>>(d, ex->b);

@@ -215,6 +215,15 @@ int orbfe_extractor_create(const orbfe_params* p, int device, int width, int hei
                 c.candBase = keyTotal;
                 c.candCap = ((cw + 1) / 2) * ((ch + 1) / 2); /* NMS survivors are never 8-adjacent */
                 keyTotal += c.candCap;
+                if (cw > 0 && ch > 0) {
+                    const int ox = iniX & 3, cx0 = ox + 3, w0 = cx0 >> 2, wl = (cx0 + cw - 1) >> 2;
+                    c.ngw = (short)(wl - w0 + 1);
+                    c.nw = (short)((ox + c.rw + 3) >> 2);
+                    c.invcw = (16777216u + cw - 1) / cw;
+                    c.invgw = (16777216u + c.ngw - 1) / c.ngw;
+                    c.edgeL = 0x80808080u << (8 * (cx0 & 3));
+                    c.edgeR = 0x80808080u >> (8 * (3 - ((cx0 + cw - 1) & 3)));
+                }
                 if (c.rw > 76 || c.rh > 76) { orbfe_set_error("internal: cell larger than the FAST tile"); delete ex; return ORBFE_E_INVALID; }
                 cells.push_back(c);
             }
@@ -224,6 +233,12 @@ int orbfe_extractor_create(const orbfe_params* p, int device, int width, int hei
             while (tabs.size() % 4) tabs.push_back(make_uint2(0, 0)); /* k_pyramid_level reads tabX four entries at a time */
             L.tabX = (int)tabs.size();
             linear_table(d.lv[l - 1].w, L.w, tabs);
+            for (int x = 0; x + 3 < L.w; x += 4)
+                if (tabs[L.tabX + x + 3].x - tabs[L.tabX + x].x > 6) {
+                    orbfe_set_error("scale factor too large for the resize kernel's 8-byte source window");
+                    delete ex;
+                    return ORBFE_E_INVALID;
+                }
             L.tabY = (int)tabs.size();
             linear_table(d.lv[l - 1].h, L.h, tabs);
         }

@@ -59,6 +59,12 @@ struct CellDesc {
     short pad;
     int candBase;     /* first candidate slot of this cell (per frame) */
     int candCap;
+    /* derived constants of the FAST kernel (host-computed so the kernel does no integer division) */
+    unsigned invcw;   /* ceil(2^24 / cw): p / cw == (p * invcw) >> 24 for p < 4900 */
+    unsigned invgw;   /* same for ngw */
+    short ngw;        /* tile words per row that overlap the candidate columns */
+    short nw;         /* tile words per row to load */
+    unsigned edgeL, edgeR; /* byte-flag masks of the first / last of those words */
 };
 
 /* Per-frame device buffers, all sized for max_batch at creation. */
