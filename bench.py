@@ -319,23 +319,26 @@ def main():
            "d2h_bytes_per_step": 2 * P * (cap * 60 + 8) + 2 * P * cap * 4}
 
     # ---- Hamming top-2 (config 5): database sharded over the ranks, NCCL all-gather of the per-shard top-2 + merge
+    from orb_slam3_detailed_comments_kor_b200 import sharding
     nq, ndb = args.hamming_queries, args.hamming_db
-    rows = ndb // world
+    lo, hi = sharding.shard_rows(ndb, world, rank)
+    rows = hi - lo
     db, q = synth.descriptors(5, ndb, nq)
     shard = DescriptorDatabase(rows, nq, device=local_rank)
-    shard.set(db[rank * rows:(rank + 1) * rows], index_base=rank * rows)
+    shard.set(db[lo:hi], index_base=lo)
     d_q = torch.from_numpy(q).cuda()
     d_part = torch.zeros((nq, 4), dtype=torch.int32, device="cuda")
-    d_all = torch.zeros((world, nq, 4), dtype=torch.int32, device="cuda")
     d_out = torch.zeros((nq, 4), dtype=torch.int32, device="cuda")
+    torch.cuda.synchronize()
+    ham_out = [d_out]
 
     def ham_step():
         if world == 1:
             shard.top2_device(d_q.data_ptr(), nq, 50, 0.9, False, d_out.data_ptr(), st)
         else:
             shard.top2_device(d_q.data_ptr(), nq, 50, 0.9, False, d_part.data_ptr(), st)
-            dist.all_gather_into_tensor(d_all, d_part)
-            M.merge_top2_device(local_rank, d_all.data_ptr(), world, nq, 50, 0.9, False, d_out.data_ptr(), st)
+            gathered = sharding.gather_top2(d_part, world)            # NCCL all-gather on the current (timed) stream
+            ham_out[0] = sharding.merge_gathered(gathered, 50, 0.9, False, device=local_rank, stream=st)
 
     for _ in range(3):
         ham_step()
@@ -346,10 +349,10 @@ def main():
     e1.record()
     barrier()
     ham_ms = max_over_ranks(e0.elapsed_time(e1) / args.steps)
-    pairs_s = nq * rows * world / (ham_ms / 1e3)
+    pairs_s = nq * ndb / (ham_ms / 1e3)
     popc_peak = 148 * 16 * float(peaks.get("sm_max_mhz", 1965.0)) * 1e6 / 8.0   # pairs/s/GPU at 8 POPC per pair
     hamming = {"value": pairs_s, "unit": "descriptor_pairs/s", "ms_per_step": ham_ms, "scaling": "strong",
-               "queries": nq, "db_rows": ndb, "shards": world, "accepted": int(d_out[:, 3].sum().item()),
+               "queries": nq, "db_rows": ndb, "shards": world, "accepted": int(ham_out[0][:, 3].sum().item()),
                "roofline": {"bound": "int_popc", "achieved": pairs_s / world, "peak": popc_peak, "unit": "pairs/s/GPU",
                             "frac": pairs_s / world / popc_peak,
                             "peak_source": "148 SM x 16 POPC/clk x sm_max_mhz / 8 POPC per pair (nominal; SURVEY.md §8d)"}}

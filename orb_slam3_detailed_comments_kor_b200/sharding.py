@@ -1,0 +1,49 @@
+"""Multi-GPU plumbing (one process per GPU, torch.distributed): how the two shardable parts of the path are split.
+
+* Frames / stereo pairs are independent: rank r processes pairs r, r+R, ... with its own extractors — no collective.
+* The map-descriptor database is split into R contiguous row ranges; every rank searches its range with
+  index_base = first global row, the per-shard top-2 records are all-gathered (NCCL on GPUs, gloo in the CPU tests)
+  and merged with the same strict-< rule a single scan applies (k_top2_merge / merge_top2_host).
+The reference is single-process (SURVEY.md §5 'Distributed communication backend: none'); this file is new."""
+import numpy as np
+
+from ._lib import MATCH_DTYPE
+
+
+def shard_rows(ndb, world, rank):
+    """Contiguous row range [lo, hi) of the database owned by `rank` (the last rank takes the remainder)."""
+    base = ndb // world
+    lo = rank * base
+    hi = ndb if rank == world - 1 else lo + base
+    return lo, hi
+
+
+def frames_for_rank(nframes, world, rank):
+    return list(range(rank, nframes, world))
+
+
+def gather_top2(local, world, group=None):
+    """local: torch int32 tensor [nq, 4] (best1, best2, idx, accepted) on the backend's device.
+    Returns the gathered [world, nq, 4] tensor in rank (= ascending global row) order."""
+    import torch
+    import torch.distributed as dist
+    if world == 1:
+        return local.unsqueeze(0)
+    out = torch.empty((world * local.shape[0],) + tuple(local.shape[1:]), dtype=local.dtype, device=local.device)
+    dist.all_gather_into_tensor(out, local.contiguous(), group=group)   # concatenated along dim 0 (gloo and NCCL agree)
+    return out.view((world,) + tuple(local.shape))
+
+
+def merge_gathered(gathered, th, ratio, strict_lt, device=None, stream=None):
+    """Merge [world, nq, 4] per-shard records.  CUDA tensors go through k_top2_merge (orbfe_top2_merge_device),
+    CPU tensors through the host statement of the same rule (used by the gloo tests)."""
+    import torch
+    from . import matcher as M
+    world, nq = gathered.shape[0], gathered.shape[1]
+    if gathered.is_cuda:
+        out = torch.empty((nq, 4), dtype=torch.int32, device=gathered.device)
+        M.merge_top2_device(gathered.device.index if device is None else device, gathered.data_ptr(), world, nq, th, ratio,
+                            strict_lt, out.data_ptr(), stream)
+        return out
+    parts = gathered.numpy().view(MATCH_DTYPE).reshape(world, nq)
+    return torch.from_numpy(M.merge_top2_host(parts, th, ratio, strict_lt).view(np.int32).reshape(nq, 4))
