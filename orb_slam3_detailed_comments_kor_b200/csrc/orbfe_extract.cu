@@ -3,7 +3,8 @@
  *
  * Stage            kernel              reference lines (src/ORBextractor.cc)       roofline
  *  pyramid         k_pyramid_level     1152-1177 (+ cv::resize, copyMakeBorder)     HBM
- *  FAST per cell   k_fast_cells        763-854   (+ cv::FAST 9/16, NMS, 20/7 retry) HBM/ALU
+ *  FAST per cell   k_fast_stream, k_fast_nms, k_fast_cells_list
+ *                                      763-854   (+ cv::FAST 9/16, NMS, 20/7 retry) integer ALU
  *  quadtree        k_quadtree          479-761                                      latency (L2 resident)
  *  ordering        k_assemble          856-872, 1100-1149                           latency
  *  blur            k_blur7             1114-1115 (+ cv::GaussianBlur 7x7 s=2)       HBM
@@ -215,6 +216,11 @@ __global__ void __launch_bounds__(256) k_blur7(const __grid_constant__ ExDesc d,
      (k) == 9 ? -3 * TP - 1 : (k) == 10 ? -2 * TP - 2 : (k) == 11 ? -TP - 3 : (k) == 12 ? -3 :              \
      (k) == 13 ? TP - 3 : (k) == 14 ? 2 * TP - 2 : 3 * TP - 1)
 
+#define RING_DX(k) ((k) == 0 ? 0 : (k) == 1 ? 1 : (k) == 2 ? 2 : (k) == 3 ? 3 : (k) == 4 ? 3 : (k) == 5 ? 3 : (k) == 6 ? 2 : (k) == 7 ? 1 : \
+                    (k) == 8 ? 0 : (k) == 9 ? -1 : (k) == 10 ? -2 : (k) == 11 ? -3 : (k) == 12 ? -3 : (k) == 13 ? -3 : (k) == 14 ? -2 : -1)
+#define RING_DY(k) ((k) == 0 ? 3 : (k) == 1 ? 3 : (k) == 2 ? 2 : (k) == 3 ? 1 : (k) == 4 ? 0 : (k) == 5 ? -1 : (k) == 6 ? -2 : (k) == 7 ? -3 : \
+                    (k) == 8 ? -3 : (k) == 9 ? -3 : (k) == 10 ? -2 : (k) == 11 ? -1 : (k) == 12 ? 0 : (k) == 13 ? 1 : (k) == 14 ? 2 : 3)
+
 static __host__ __device__ __forceinline__ bool run9(uint32_t m) {
     m |= m << 16;
     uint32_t x = m & (m >> 1);
@@ -227,25 +233,17 @@ static __host__ __device__ __forceinline__ bool run9(uint32_t m) {
 /* corner at threshold t  <=>  9 contiguous ring pixels all > v+t or all < v-t.
  * Masks are gathered with one funnel shift per ring pixel: (B << 1) | sign(v + t - p) collects "p > v+t" (the bit
  * order comes out reversed, which a circular run test does not care about). */
-static __host__ __device__ __forceinline__ bool fast_is_corner(const uint8_t* c, int t) {
-    const int v = c[0];
+static __host__ __device__ __forceinline__ bool fast_is_corner_vals(int v, const int (&r)[16], int t) {
     const int hi = v + t, lo = v - t;
-    const int p0 = c[RING_OFF(0, FAST_TP)], p8 = c[RING_OFF(8, FAST_TP)];
-    const int p4 = c[RING_OFF(4, FAST_TP)], p12 = c[RING_OFF(12, FAST_TP)];
-    /* any 9-arc contains one pixel of every opposite pair (k, k+8) */
-    const bool mayB = (p0 > hi || p8 > hi) && (p4 > hi || p12 > hi);
-    const bool mayD = (p0 < lo || p8 < lo) && (p4 < lo || p12 < lo);
-    if (!(mayB || mayD)) return false;
     uint32_t B = 0, D = 0;
 #pragma unroll
     for (int k = 0; k < 16; k++) {
-        const int p = c[RING_OFF(k, FAST_TP)];
 #ifdef __CUDA_ARCH__
-        B = __funnelshift_l((uint32_t)(hi - p), B, 1);   /* sign bit set <=> p > hi */
-        D = __funnelshift_l((uint32_t)(p - lo), D, 1);   /* sign bit set <=> p < lo */
+        B = __funnelshift_l((uint32_t)(hi - r[k]), B, 1);   /* sign bit set <=> r > hi */
+        D = __funnelshift_l((uint32_t)(r[k] - lo), D, 1);   /* sign bit set <=> r < lo */
 #else
-        B = (B << 1) | ((uint32_t)(hi - p) >> 31);
-        D = (D << 1) | ((uint32_t)(p - lo) >> 31);
+        B = (B << 1) | ((uint32_t)(hi - r[k]) >> 31);
+        D = (D << 1) | ((uint32_t)(r[k] - lo) >> 31);
 #endif
     }
     return run9(B) || run9(D);
@@ -256,11 +254,7 @@ static __host__ __device__ __forceinline__ bool fast_is_corner(const uint8_t* c,
  * m = max(v - min_arcs(max_arc r), max_arcs(min_arc r) - v).  Besides being cheaper this keeps every min/max
  * operand a plain non-negated register: nvcc 12.9 folds a negation into VIMNMX3 on sm_100a and the result
  * loses the sign (found by tools/fast_device_test3.cu: max(m, max(lo, -hi)) returned max(m, lo, hi)). */
-static __host__ __device__ __forceinline__ int fast_score(const uint8_t* c) {
-    const int v = c[0];
-    int r[16];
-#pragma unroll
-    for (int k = 0; k < 16; k++) r[k] = (int)c[RING_OFF(k, FAST_TP)];
+static __host__ __device__ __forceinline__ int fast_score_vals(int v, const int (&r)[16]) {
     int lo2[16], hi2[16], lo4[16], hi4[16];
 #pragma unroll
     for (int k = 0; k < 16; k++) { lo2[k] = min(r[k], r[(k + 1) & 15]); hi2[k] = max(r[k], r[(k + 1) & 15]); }
@@ -278,6 +272,20 @@ static __host__ __device__ __forceinline__ int fast_score(const uint8_t* c) {
     return (dark > bright ? dark : bright) - 1;
 }
 
+/* the same on a pixel of a FAST_TP-pitch tile */
+static __host__ __device__ __forceinline__ bool fast_is_corner(const uint8_t* c, int t) {
+    int r[16];
+#pragma unroll
+    for (int k = 0; k < 16; k++) r[k] = (int)c[RING_OFF(k, FAST_TP)];
+    return fast_is_corner_vals(c[0], r, t);
+}
+static __host__ __device__ __forceinline__ int fast_score(const uint8_t* c) {
+    int r[16];
+#pragma unroll
+    for (int k = 0; k < 16; k++) r[k] = (int)c[RING_OFF(k, FAST_TP)];
+    return fast_score_vals(c[0], r);
+}
+
 /* Sieve for four horizontally adjacent pixels at once (one 32-bit word of the tile): with a = |I(x,y+3) - I|,
  * b = |I(x,y-3) - I|, r = |I(x+3,y) - I|, l = |I(x-3,y) - I| (VABSDIFF4, one instruction per four pixels), a corner at
  * threshold t needs (a > t or b > t) and (r > t or l > t): every 9-arc of the ring holds one pixel of each opposite
@@ -290,12 +298,14 @@ static __device__ __forceinline__ uint32_t fast_sieve4(uint32_t c, uint32_t top,
 }
 
 #define FAST_LISTCAP (70 * 70)
-/* One CTA = one 35-px-grid cell of one level of one frame: cv::FAST(roi, iniTh) -> if empty cv::FAST(roi, minTh),
- * with NMS seeing only this cell's scores at the current threshold (SURVEY.md §7 hard part 2).
+/* Fallback path of the cell stage.  One CTA = one 35-px-grid cell of one level of one frame, processed from its pixels:
+ * cv::FAST(roi, th) with NMS seeing only this cell's scores at that threshold (SURVEY.md §7 hard part 2).  It runs only
+ * for the cells that came out empty at iniTh (k_fast_stream + k_fast_nms) and redoes them at minTh
+ * (src/ORBextractor.cc:825-828); persistent CTAs walk the list those kernels left in b.fbList.
  * Work is funnelled through compacted lists so that each stage runs dense:
  *   sieve (4 px per thread-step, all candidates) -> list1 -> exact 9-of-16 test -> list2 -> score -> NMS -> bitmask.
  * Output: the cell's keypoints in (y, x) order, packed, at the cell's slot range. */
-__global__ void __launch_bounds__(FAST_NT, 8) k_fast_cells(const __grid_constant__ ExDesc d, ExBuffers b) {
+static __device__ void fast_cell_from_pixels(const ExDesc& d, const ExBuffers& b, const int cellIdx, const size_t f, int th, const int npass) {
     /* dynamic smem, sized for the largest cell of this extractor: tile | score tile | list1 | list2 | mask */
     extern __shared__ __align__(16) uint8_t s_dyn[];
     uint8_t* s_img = s_dyn;
@@ -306,9 +316,8 @@ __global__ void __launch_bounds__(FAST_NT, 8) k_fast_cells(const __grid_constant
     __shared__ int s_n1, s_n2, s_total;
     __shared__ int s_wsum[FAST_NT / 32];
 
-    const CellDesc cell = b.cells[blockIdx.x];
-    const size_t f = blockIdx.y;
-    int* countOut = b.cellCount + f * d.nCells + blockIdx.x;
+    const CellDesc cell = b.cells[cellIdx];
+    int* countOut = b.cellCount + f * d.nCells + cellIdx;
     const int cw = cell.rw - 6, ch = cell.rh - 6;
     if (cw <= 0 || ch <= 0) {
         if (threadIdx.x == 0) *countOut = 0;
@@ -336,8 +345,7 @@ __global__ void __launch_bounds__(FAST_NT, 8) k_fast_cells(const __grid_constant
     const int cx0 = ox + 3, w0 = cx0 >> 2, ngw = cell.ngw;
     const uint32_t invgw = cell.invgw;
     const int nitems = ch * ngw;
-    int th = d.iniTh;
-    for (int pass = 0; pass < 2; pass++) {
+    for (int pass = 0; pass < npass; pass++) {
         if (threadIdx.x == 0) { s_n1 = 0; s_n2 = 0; }
         for (int i = threadIdx.x; i < nwords; i += FAST_NT) s_mask[i] = 0;
         __syncthreads();
@@ -436,7 +444,7 @@ __global__ void __launch_bounds__(FAST_NT, 8) k_fast_cells(const __grid_constant
         if (threadIdx.x == FAST_NT - 1) s_total = wbase + incl;
         __syncthreads();
         const int total = s_total;
-        if (total > 0 || pass == 1) {
+        if (total > 0 || pass == npass - 1) {
             int k = wbase + incl - mine;
             uint32_t* out = b.cand + f * d.candCap + cell.candBase;
             for (int i = wbeg; i < wend; i++) {
@@ -461,6 +469,221 @@ __global__ void __launch_bounds__(FAST_NT, 8) k_fast_cells(const __grid_constant
         }
         th = d.minTh;
         __syncthreads();
+    }
+}
+
+/* Persistent CTAs re-detect, at minTh, the cells listed in b.fbList (entry = frame * nCells + cell). */
+__global__ void __launch_bounds__(FAST_NT, 8) k_fast_cells_list(const __grid_constant__ ExDesc d, ExBuffers b) {
+    const int n = *b.fbCount;
+    for (int i = blockIdx.x; i < n; i += gridDim.x) {
+        const int id = b.fbList[i];
+        const int f = id / d.nCells;
+        fast_cell_from_pixels(d, b, id - f * d.nCells, (size_t)f, d.minTh, 1);
+        __syncthreads();
+    }
+}
+
+/* ---- streaming detector: the iniTh pass over whole levels ------------------------------------------------------ */
+#define FS_WARPS 4
+#define FS_R 8          /* rows per compaction chunk */
+#define FS_COLS 120     /* candidate columns per strip (lanes 1..30; lanes 0 and 31 carry the 4 px halos) */
+
+/* One warp = one strip (120 columns x up to 48 rows) of one level of one frame; warps are independent (no block
+ * barrier).  Each lane owns four adjacent columns.  Per row the warp loads the row three below (coalesced 128 B),
+ * keeps the last 16 rows in a shared-memory ring, and runs the 4-pixel sieve on registers (left/right neighbours come
+ * by shuffle).  Every FS_R rows the sieve's survivors are compacted (per-lane counts, one warp scan) into a queue,
+ * the exact 9-of-16 test runs densely over the queue (corners compacted in place), scores are computed for the corners
+ * and each corner (x, y, score) is appended to the raw list of the 35-px cell that contains it (one global atomic).
+ * k_fast_nms then does the cell-local non-maximum suppression and ordering. */
+#define FS_BROWS (FS_R + 6)   /* rows yc-3 .. yc+FS_R+2 of the current chunk */
+#define FS_PW 33               /* words per buffered row: 32 + 1 so that equal columns of different rows hit different banks */
+__global__ void __launch_bounds__(FS_WARPS * 32) k_fast_stream(const __grid_constant__ ExDesc d, ExBuffers b) {
+    __shared__ __align__(16) uint32_t s_buf[FS_WARPS][FS_BROWS][FS_PW];
+    __shared__ uint32_t s_hits[FS_WARPS][FS_R][32];
+    __shared__ uint16_t s_q[FS_WARPS][FS_R * FS_COLS + 32];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const size_t f = blockIdx.y;
+    if (blockIdx.x == 0 && threadIdx.x == 0 && f == 0) *b.fbCount = 0; /* list of empty cells restarts every batch */
+    const int sidx = blockIdx.x * FS_WARPS + warp;
+    if (sidx >= d.nStrips) return;
+    const StripDesc sd = b.strips[sidx];
+    const LevelDesc& L = d.lv[sd.level];
+    const int pitch = L.pitch, th = d.iniTh;
+    const int col = sd.xs - 4 + 4 * lane;                       /* level x of my word's byte 0 */
+    const int colc = min(col, (L.w + ORBFE_EDGE - 4) & ~3);     /* keep the load inside the padded row */
+    const int y0 = sd.y0, nrows = sd.nrows;
+    /* p walks down the level: it always points at the next row to fetch (row yc + r + 3) */
+    const uint8_t* p = b.pyr + f * d.pyrSlab + (uint32_t)(L.pyrOff + (ORBFE_EDGE + y0 - 3) * pitch + ORBFE_ROW_LEAD + colc);
+    uint32_t* buf = &s_buf[warp][0][0];
+    const uint8_t* bufb = reinterpret_cast<const uint8_t*>(buf) + 3 * (4 * FS_PW);   /* row yc of the chunk */
+    uint16_t* q = s_q[warp];
+    uint32_t vmask = 0;
+#pragma unroll
+    for (int k = 0; k < 4; k++)
+        if (lane >= 1 && lane <= 30 && col + k >= ORBFE_EDGE && col + k < L.w - ORBFE_EDGE) vmask |= 0x80u << (8 * k);
+#pragma unroll
+    for (int r = 0; r < 6; r++, p += pitch) buf[r * FS_PW + lane] = __ldg(reinterpret_cast<const uint32_t*>(p));   /* rows y0-3 .. y0+2 */
+    const uint32_t k127mt = (uint32_t)(127 - th) * 0x01010101u;
+    int* rawCount = b.rawCount + f * d.nCells;
+    uint32_t* raw = b.raw + f * (size_t)d.rawCap;
+    for (int c0 = 0; c0 < nrows; c0 += FS_R) {
+        const int rows = min(FS_R, nrows - c0);
+        __syncwarp();
+        /* 1. sieve, one row per step: buffer rows r (y-3), r+3 (y), r+6 (y+3, fetched now) */
+        for (int r = 0; r < rows; r++, p += pitch) {
+            const uint32_t top = __ldg(reinterpret_cast<const uint32_t*>(p));
+            buf[(r + 6) * FS_PW + lane] = top;
+            const uint32_t cen = buf[(r + 3) * FS_PW + lane], bot = buf[r * FS_PW + lane];
+            const uint32_t lw = __shfl_up_sync(0xFFFFFFFFu, cen, 1), rw = __shfl_down_sync(0xFFFFFFFFu, cen, 1);
+            s_hits[warp][r][lane] = fast_sieve4(cen, top, bot, __byte_perm(lw, cen, 0x4321), __byte_perm(cen, rw, 0x6543), k127mt) & vmask;
+        }
+        __syncwarp();
+        /* 2. compaction: lane counts the survivors of its columns over the chunk, one scan gives its queue offset */
+        int cnt = 0;
+        for (int r = 0; r < rows; r++) cnt += __popc(s_hits[warp][r][lane]);
+        int incl = cnt;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+            if (lane >= o) incl += t;
+        }
+        const int n = __shfl_sync(0xFFFFFFFFu, incl, 31);
+        if (n > 0) {
+            int off = incl - cnt;
+            for (int r = 0; r < rows; r++) {
+                uint32_t h = s_hits[warp][r][lane];
+                while (h) {
+                    const int bit = __ffs(h) - 1;
+                    h &= h - 1;
+                    q[off++] = (uint16_t)(r * (4 * FS_PW) + 4 * lane + (bit >> 3));     /* byte offset of the pixel from bufb */
+                }
+            }
+            __syncwarp();
+            /* 3. exact test over the queue; corners are written back at the front of the queue */
+            int m = 0;
+            for (int e0 = 0; e0 < n; e0 += 32) {
+                const int e = e0 + lane;
+                bool isc = false;
+                uint32_t ent = 0;
+                if (e < n) {
+                    ent = q[e];
+                    const uint8_t* c = bufb + ent;
+                    int rv[16];
+#pragma unroll
+                    for (int k = 0; k < 16; k++) rv[k] = c[RING_OFF(k, (4 * FS_PW))];
+                    isc = fast_is_corner_vals(c[0], rv, th);
+                }
+                const uint32_t bal = __ballot_sync(0xFFFFFFFFu, isc);
+                if (isc) q[m + __popc(bal & ((1u << lane) - 1))] = (uint16_t)ent;   /* m <= e0: never ahead of the reads */
+                m += __popc(bal);
+                __syncwarp();
+            }
+            /* 4. scores, and hand every corner to its cell */
+            for (int e = lane; e < m; e += 32) {
+                const uint32_t ent = q[e];
+                const uint8_t* c = bufb + ent;
+                int rv[16];
+#pragma unroll
+                for (int k = 0; k < 16; k++) rv[k] = c[RING_OFF(k, (4 * FS_PW))];
+                const int sc = fast_score_vals(c[0], rv);
+                const int er = (int)ent / (4 * FS_PW);
+                const int x = sd.xs - 4 + ((int)ent - er * (4 * FS_PW)), y = y0 + c0 + er;
+                const int cj = (int)(((uint32_t)(x - ORBFE_EDGE) * L.invW) >> 24), ci = (int)(((uint32_t)(y - ORBFE_EDGE) * L.invH) >> 24);
+                const int cell = ci * L.nCols + cj;
+                const int slot = atomicAdd(&rawCount[L.cellBase + cell], 1);
+                raw[L.rawBase + cell * L.rawStride + slot] = (uint32_t)(x - ORBFE_MIN_BORDER) | ((uint32_t)(y - ORBFE_MIN_BORDER) << 12) | ((uint32_t)sc << 24);
+            }
+            __syncwarp();
+        }
+        /* 5. the last six rows of this chunk are the first six of the next */
+        if (c0 + FS_R < nrows) {
+            uint32_t keep[6];
+#pragma unroll
+            for (int r = 0; r < 6; r++) keep[r] = buf[(FS_R + r) * FS_PW + lane];
+#pragma unroll
+            for (int r = 0; r < 6; r++) buf[r * FS_PW + lane] = keep[r];
+        }
+    }
+}
+
+/* One CTA (64 threads) = one cell: scatter the cell's raw corners into a zeroed score tile, keep the strict local maxima
+ * (cv::FAST nonmaxSuppression: neighbours outside the cell's candidate area or below the threshold count as 0), write
+ * them in (y, x) order.  A cell that ends up empty is queued for the minTh fallback (k_fast_cells_list). */
+#define FN_NT 64
+#define FN_TP 72
+__global__ void __launch_bounds__(FN_NT) k_fast_nms(const __grid_constant__ ExDesc d, ExBuffers b) {
+    __shared__ __align__(16) uint8_t s_sc[FN_TP * FN_TP];
+    __shared__ uint32_t s_mask[(FAST_LISTCAP + 31) / 32 + 1];
+    const int cellIdx = blockIdx.x;
+    const size_t f = blockIdx.y;
+    const CellDesc cell = b.cells[cellIdx];
+    int* countOut = b.cellCount + f * d.nCells + cellIdx;
+    const int cw = cell.rw - 6, ch = cell.rh - 6;
+    if (cw <= 0 || ch <= 0) {
+        if (threadIdx.x == 0) *countOut = 0;
+        return;
+    }
+    int* rawCountP = b.rawCount + f * d.nCells + cellIdx;
+    const int n = *rawCountP;
+    const LevelDesc& L = d.lv[cell.level];
+    const uint32_t* raw = b.raw + f * (size_t)d.rawCap + L.rawBase + (cellIdx - L.cellBase) * L.rawStride;
+    int total = 0;
+    if (n > 0) {
+        const int tp = (cw + 2 + 7) & ~7, nwords = (cw * ch + 31) >> 5;
+        for (int i = threadIdx.x; i < (ch + 2) * tp / 8; i += FN_NT) reinterpret_cast<uint2*>(s_sc)[i] = make_uint2(0, 0);
+        for (int i = threadIdx.x; i < nwords; i += FN_NT) s_mask[i] = 0;
+        __syncthreads();
+        const int bx = 3 + cell.xoff - 1, by = 3 + cell.yoff - 1; /* raw x,y are relative to the 16 px border; tile has a 1 px apron */
+        for (int e = threadIdx.x; e < n; e += FN_NT) {
+            const uint32_t p = raw[e];
+            s_sc[(int)(((p >> 12) & 0xFFF) - by) * tp + (int)((p & 0xFFF) - bx)] = (uint8_t)(p >> 24);
+        }
+        __syncthreads();
+        for (int e = threadIdx.x; e < n; e += FN_NT) {
+            const uint32_t p = raw[e];
+            const int px = (int)(p & 0xFFF) - bx, py = (int)((p >> 12) & 0xFFF) - by;   /* 1-based inside the tile */
+            const uint8_t* sc = s_sc + py * tp + px;
+            const int v = sc[0];
+            const int nb = max(max(max((int)sc[-tp - 1], (int)sc[-tp]), max((int)sc[-tp + 1], (int)sc[-1])),
+                               max(max((int)sc[1], (int)sc[tp - 1]), max((int)sc[tp], (int)sc[tp + 1])));
+            if (v > nb) {
+                const int pi = (py - 1) * cw + (px - 1);
+                atomicOr(&s_mask[pi >> 5], 1u << (pi & 31));
+            }
+        }
+        __syncthreads();
+        if (threadIdx.x < 32) {
+            /* ordered output by one warp: lane owns a contiguous run of mask words */
+            const int lane = threadIdx.x, per = (nwords + 31) >> 5;
+            const int wbeg = min(lane * per, nwords), wend = min(wbeg + per, nwords);
+            int mine = 0;
+            for (int i = wbeg; i < wend; i++) mine += __popc(s_mask[i]);
+            int incl = mine;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+                if (lane >= o) incl += t;
+            }
+            total = __shfl_sync(0xFFFFFFFFu, incl, 31);
+            int k = incl - mine;
+            uint32_t* out = b.cand + f * d.candCap + cell.candBase;
+            const uint32_t invcw = cell.invcw;
+            for (int i = wbeg; i < wend; i++) {
+                uint32_t mm = s_mask[i];
+                while (mm) {
+                    const int bit = __ffs(mm) - 1;
+                    mm &= mm - 1;
+                    const int pi = i * 32 + bit;
+                    const int py = (int)(((uint32_t)pi * invcw) >> 24), px = pi - py * cw;
+                    out[k++] = (uint32_t)(px + 3 + cell.xoff) | ((uint32_t)(py + 3 + cell.yoff) << 12) | ((uint32_t)s_sc[(py + 1) * tp + px + 1] << 24);
+                }
+            }
+        }
+    }
+    if (threadIdx.x == 0) {
+        *countOut = total;
+        *rawCountP = 0;                                   /* ready for the next batch */
+        if (total == 0) b.fbList[atomicAdd(b.fbCount, 1)] = (int)f * d.nCells + cellIdx;
     }
 }
 
@@ -959,7 +1182,7 @@ int orbfe_collect_stage_times(orbfe_extractor* ex);
 
 int orbfe_configure_kernels(int quadSmem, int fastSmem) {
     ORBFE_CUDA(cudaFuncSetAttribute(k_quadtree, cudaFuncAttributeMaxDynamicSharedMemorySize, quadSmem));
-    ORBFE_CUDA(cudaFuncSetAttribute(k_fast_cells, cudaFuncAttributeMaxDynamicSharedMemorySize, fastSmem));
+    ORBFE_CUDA(cudaFuncSetAttribute(k_fast_cells_list, cudaFuncAttributeMaxDynamicSharedMemorySize, fastSmem));
     return 0;
 }
 
@@ -982,7 +1205,9 @@ int orbfe_launch_extract(orbfe_extractor* ex, const uint8_t* d_images, int nfram
         k_pyramid_level<<<dim3(intWarps + 1, (L.h + 2 * ORBFE_EDGE + 7) / 8, nframes), dim3(32, 8), 0, st>>>(d, ex->b, l);
     }
     STAGE_MARK();
-    k_fast_cells<<<dim3(d.nCells, nframes), FAST_NT, ex->fastSmem, st>>>(d, ex->b);
+    k_fast_stream<<<dim3((d.nStrips + FS_WARPS - 1) / FS_WARPS, nframes), FS_WARPS * 32, 0, st>>>(d, ex->b);
+    k_fast_nms<<<dim3(d.nCells, nframes), FN_NT, 0, st>>>(d, ex->b);
+    k_fast_cells_list<<<148 * 4, FAST_NT, ex->fastSmem, st>>>(d, ex->b);
     STAGE_MARK();
     for (int l = 0; l < d.nlevels; l++) {
         const LevelDesc& L = d.lv[l];
@@ -997,7 +1222,7 @@ int orbfe_launch_extract(orbfe_extractor* ex, const uint8_t* d_images, int nfram
     STAGE_MARK();
 #undef STAGE_MARK
     if (prof) ex->stagePending = 1;
-    ex->launches += 2 * d.nlevels + 4;
+    ex->launches += 2 * d.nlevels + 6;
     ORBFE_CUDA(cudaGetLastError());
     return 0;
 }

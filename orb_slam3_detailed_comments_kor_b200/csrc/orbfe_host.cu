@@ -158,6 +158,8 @@ int orbfe_extractor_create(const orbfe_params* p, int device, int width, int hei
     ExDesc& d = ex->d;
     d.nlevels = nl; d.W = width; d.H = height; d.iniTh = p->ini_th_fast; d.minTh = p->min_th_fast;
     std::vector<CellDesc> cells;
+    std::vector<StripDesc> strips;
+    int rawTotal = 0;
     std::vector<uint2> tabs;
     size_t pyrOff = 0, blurOff = 0;
     int keyTotal = 0, selTotal = 0, nodeCap = 64;
@@ -228,6 +230,18 @@ int orbfe_extractor_create(const orbfe_params* p, int device, int width, int hei
                 cells.push_back(c);
             }
         L.keyCap = keyTotal - L.keyBase;
+        L.invW = (16777216u + L.wCell - 1) / L.wCell;
+        L.invH = (16777216u + L.hCell - 1) / L.hCell;
+        L.rawBase = rawTotal;
+        L.rawStride = L.wCell * L.hCell;
+        rawTotal += L.nCols * L.nRows * L.rawStride;
+        for (int y0 = ORBFE_EDGE; y0 < L.h - ORBFE_EDGE; y0 += 48)
+            for (int xs = ORBFE_MIN_BORDER; xs < L.w - ORBFE_EDGE; xs += 120) {
+                StripDesc sd;
+                sd.level = (short)l; sd.xs = (short)xs; sd.y0 = (short)y0;
+                sd.nrows = (short)std::min(48, L.h - ORBFE_EDGE - y0);
+                strips.push_back(sd);
+            }
         nodeCap = std::max(nodeCap, std::max(L.selCap, std::max(L.nIni, L.nCols * L.nRows)));
         if (l > 0) {
             while (tabs.size() % 4) tabs.push_back(make_uint2(0, 0)); /* k_pyramid_level reads tabX four entries at a time */
@@ -253,6 +267,8 @@ int orbfe_extractor_create(const orbfe_params* p, int device, int width, int hei
     d.nodeCap = cap2;
     d.nCells = (int)cells.size();
     d.candCap = keyTotal;
+    d.nStrips = (int)strips.size();
+    d.rawCap = rawTotal;
     d.kpCap = selTotal;
     d.pyrSlab = align_up(pyrOff + 256, 256);
     d.blurSlab = align_up(blurOff + 256, 256);
@@ -272,6 +288,7 @@ int orbfe_extractor_create(const orbfe_params* p, int device, int width, int hei
     const size_t B = (size_t)max_batch;
     ExBuffers& b = ex->b;
     CellDesc* dCells = nullptr;
+    StripDesc* dStrips = nullptr;
     uint2* dTabs = nullptr;
 #define TRY(x) do { rc = (x); if (rc) { orbfe_extractor_destroy(ex); return rc; } } while (0)
 #define TRYC(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { rc = orbfe_cuda_fail(e_, #x); orbfe_extractor_destroy(ex); return rc; } } while (0)
@@ -294,9 +311,18 @@ int orbfe_extractor_create(const orbfe_params* p, int device, int width, int hei
     TRY(dev_alloc(ex, &b.depth, B * d.kpCap));
     TRY(dev_alloc(ex, &b.sadBest, B * d.kpCap));
     TRY(dev_alloc(ex, &dCells, cells.size()));
+    TRY(dev_alloc(ex, &dStrips, strips.size()));
+    TRY(dev_alloc(ex, &b.raw, B * (size_t)d.rawCap));
+    TRY(dev_alloc(ex, &b.rawCount, B * d.nCells));
+    TRY(dev_alloc(ex, &b.fbList, B * d.nCells));
+    TRY(dev_alloc(ex, &b.fbCount, 1));
     TRY(dev_alloc(ex, &dTabs, tabs.size()));
     TRY(dev_alloc(ex, &ex->inputStage, B * (size_t)width * height));
     b.cells = dCells;
+    b.strips = dStrips;
+    TRYC(cudaMemcpy(dStrips, strips.data(), strips.size() * sizeof(StripDesc), cudaMemcpyHostToDevice));
+    TRYC(cudaMemset(b.rawCount, 0, B * d.nCells * sizeof(int)));
+    TRYC(cudaMemset(b.fbCount, 0, sizeof(int)));
     b.tabs = dTabs;
     b.input = ex->inputStage;
     TRYC(cudaMemcpy(dCells, cells.data(), cells.size() * sizeof(CellDesc), cudaMemcpyHostToDevice));

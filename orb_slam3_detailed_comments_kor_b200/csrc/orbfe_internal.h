@@ -33,6 +33,9 @@ struct LevelDesc {
     int tabX, tabY;  /* resize coefficient tables (uint2 entries) for producing this level from level-1 */
     float scale;     /* mvScaleFactor[level] */
     float kpSize;    /* (float)(int)(31*scale), src/ORBextractor.cc:862 */
+    unsigned invW, invH; /* ceil(2^24 / wCell), ceil(2^24 / hCell): cell of a candidate pixel without a division */
+    int rawBase;     /* first raw-corner slot of this level (per frame) */
+    int rawStride;   /* raw-corner slots per cell = wCell * hCell */
 };
 
 struct ExDesc {
@@ -43,6 +46,8 @@ struct ExDesc {
     int kpCap;        /* selected keypoints per frame, all levels (= sum selCap) */
     int nodeCap;      /* quadtree node capacity (max over levels of selCap, padded) */
     int iniTh, minTh;
+    int nStrips;      /* strips of k_fast_stream per frame */
+    int rawCap;       /* raw-corner slots per frame */
     int fastRows;     /* tallest FAST cell ROI (rows of the smem tile) */
     int fastPix;      /* most candidate pixels in one cell, rounded up to a multiple of 8 */
     size_t pyrSlab;   /* bytes per frame */
@@ -67,12 +72,22 @@ struct CellDesc {
     unsigned edgeL, edgeR; /* byte-flag masks of the first / last of those words */
 };
 
+/* One warp-sized piece of a level for k_fast_stream: candidate columns [xs, xs+120), rows [y0, y0+nrows). */
+struct StripDesc {
+    short level, xs, y0, nrows;
+};
+
 /* Per-frame device buffers, all sized for max_batch at creation. */
 struct ExBuffers {
     uint8_t* pyr;        /* [B][pyrSlab] */
     uint8_t* blur;       /* [B][blurSlab] */
     uint32_t* cand;      /* [B][candCap]  packed x | y<<12 | score<<24, coordinates relative to minBorder */
     int* cellCount;      /* [B][nCells] */
+    uint32_t* raw;       /* [B][rawCap]   corners at iniTh before NMS, per cell at rawBase + cell*rawStride */
+    int* rawCount;       /* [B][nCells]   zero between batches (k_fast_nms resets what it consumes) */
+    int* fbList;         /* [B*nCells]    cells that came out empty at iniTh */
+    int* fbCount;        /* [1] */
+    const StripDesc* strips;
     uint32_t* keys;      /* [B][candCap]  quadtree scratch: a level's candidates gathered in cell order */
     uint16_t* keyNode;   /* [B][candCap]  quadtree scratch: node of each candidate */
     uint32_t* sel;       /* [B][kpCap]    quadtree output, packed like cand, per level at selBase */
