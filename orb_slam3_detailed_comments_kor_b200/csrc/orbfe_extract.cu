@@ -73,13 +73,15 @@ static __device__ __forceinline__ uint32_t resize_px_generic(const uint8_t* r0, 
     return (uint32_t)((((b0 * (h0 >> 4)) >> 16) + ((b1 * (h1 >> 4)) >> 16) + 2) >> 2);
 }
 
+#define PYR_ROWS 2   /* output rows per thread: the horizontal tables, selectors and shifts are shared between them */
 __global__ void __launch_bounds__(256) k_pyramid_level(const __grid_constant__ ExDesc d, ExBuffers b, int level) {
-    /* block = 32 x 8: a warp works on one output row.  Warps [0, nInteriorWarps) take the groups that lie fully inside
-     * the image (fast path, no divergence); the last warp of the row takes every group that touches the border. */
+    /* block = 32 x 8: a warp works on PYR_ROWS consecutive output rows.  Warps [0, nInteriorWarps) take the groups that
+     * lie fully inside the image (fast path, no divergence); the last warp takes every group that touches the border. */
     const LevelDesc& L = d.lv[level];
     const LevelDesc& P = d.lv[level - 1];
-    const int row = blockIdx.y * 8 + threadIdx.y;
-    if (row >= L.h + 2 * ORBFE_EDGE) return;
+    const int nrows = L.h + 2 * ORBFE_EDGE;
+    const int row0 = (blockIdx.y * 8 + threadIdx.y) * PYR_ROWS;
+    if (row0 >= nrows) return;
     const int groups = L.pitch >> 2;
     const int gFirst = ORBFE_ROW_LEAD / 4, nInt = L.w >> 2;     /* interior groups: px0 = 0, 4, ... */
     const int tx = blockIdx.x * 32 + threadIdx.x;
@@ -98,44 +100,56 @@ __global__ void __launch_bounds__(256) k_pyramid_level(const __grid_constant__ E
     }
     const size_t f = blockIdx.z;
     uint8_t* slab = b.pyr + f * d.pyrSlab;
-    const int yi = reflect101(row - ORBFE_EDGE, L.h);
-    const uint2 yt = __ldg(b.tabs + L.tabY + yi);
-    /* row yt.x+1 and column sx+1 may be the source's own border: their coefficient is then 0 */
-    const uint8_t* r0 = slab + (uint32_t)(P.pyrOff + (ORBFE_EDGE + (int)yt.x) * P.pitch + ORBFE_ROW_LEAD);
-    const uint8_t* r1 = r0 + P.pitch;
-    const int b0 = yt.y & 0xFFFF, b1 = yt.y >> 16;
+    const uint8_t* sint = slab + (uint32_t)(P.pyrOff + ORBFE_EDGE * P.pitch + ORBFE_ROW_LEAD);
     const int px0 = g * 4 - ORBFE_ROW_LEAD;
-    uint32_t out = 0;
+    uint8_t* dstp = slab + (uint32_t)(L.pyrOff + row0 * L.pitch + g * 4);
     if (interior) {
         const uint4* tp = reinterpret_cast<const uint4*>(b.tabs + L.tabX + px0); /* tabX is 4-entry aligned */
         const uint4 ta = __ldg(tp), tb = __ldg(tp + 1); /* entries (sx, c0|c1<<16) of the four pixels */
         const uint32_t sx0 = ta.x;
         const uint32_t base = sx0 & ~3u, sh = (sx0 & 3u) * 8;
-        const uint32_t* q0 = reinterpret_cast<const uint32_t*>(r0 + base);
-        const uint32_t* q1 = reinterpret_cast<const uint32_t*>(r1 + base);
-        const uint32_t a0 = q0[0], a1 = q0[1], a2 = q0[2], c0w = q1[0], c1w = q1[1], c2w = q1[2];
-        const uint32_t u0 = __funnelshift_r(a0, a1, sh), u1 = __funnelshift_r(a1, a2, sh); /* bytes sx0 .. sx0+7 of row 0 */
-        const uint32_t v0 = __funnelshift_r(c0w, c1w, sh), v1 = __funnelshift_r(c1w, c2w, sh);
-        const uint32_t sxs[4] = {ta.x, ta.z, tb.x, tb.z};
         const uint32_t cfs[4] = {ta.y, ta.w, tb.y, tb.w};
+        /* byte selectors (off, off+1) -> low half; off = sx - sx0 in 0..6 (host-checked): four taps within 8 bytes */
+        const uint32_t sel[4] = {0x10u, (ta.z - sx0) * 0x11u + 0x10u, (tb.x - sx0) * 0x11u + 0x10u, (tb.z - sx0) * 0x11u + 0x10u};
 #pragma unroll
-        for (int k = 0; k < 4; k++) {
-            const uint32_t off = sxs[k] - sx0;            /* 0..6 (host-checked): four taps within 8 bytes */
-            const uint32_t sel = off * 0x11u + 0x10u;     /* bytes (off, off+1) -> low half */
-            const uint32_t h0 = __dp2a_lo(cfs[k], __byte_perm(u0, u1, sel), 0u);
-            const uint32_t h1 = __dp2a_lo(cfs[k], __byte_perm(v0, v1, sel), 0u);
-            const uint32_t v = (uint32_t)((((b0 * (int)(h0 >> 4)) >> 16) + ((b1 * (int)(h1 >> 4)) >> 16) + 2) >> 2);
-            out |= v << (8 * k);
+        for (int rr = 0; rr < PYR_ROWS; rr++) {
+            if (row0 + rr >= nrows) break;
+            const uint2 yt = __ldg(b.tabs + L.tabY + reflect101(row0 + rr - ORBFE_EDGE, L.h));
+            /* row yt.x+1 and column sx+1 may be the source's own border: their coefficient is then 0 */
+            const uint32_t* q0 = reinterpret_cast<const uint32_t*>(sint + (uint32_t)((int)yt.x * P.pitch) + base);
+            const uint32_t* q1 = reinterpret_cast<const uint32_t*>(reinterpret_cast<const uint8_t*>(q0) + P.pitch);
+            const int b0 = yt.y & 0xFFFF, b1 = yt.y >> 16;
+            const uint32_t a0 = q0[0], a1 = q0[1], a2 = q0[2], c0w = q1[0], c1w = q1[1], c2w = q1[2];
+            const uint32_t u0 = __funnelshift_r(a0, a1, sh), u1 = __funnelshift_r(a1, a2, sh); /* bytes sx0 .. sx0+7 of row 0 */
+            const uint32_t v0 = __funnelshift_r(c0w, c1w, sh), v1 = __funnelshift_r(c1w, c2w, sh);
+            uint32_t out = 0;
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                const uint32_t h0 = __dp2a_lo(cfs[k], __byte_perm(u0, u1, sel[k]), 0u);
+                const uint32_t h1 = __dp2a_lo(cfs[k], __byte_perm(v0, v1, sel[k]), 0u);
+                const uint32_t v = (uint32_t)((((b0 * (int)(h0 >> 4)) >> 16) + ((b1 * (int)(h1 >> 4)) >> 16) + 2) >> 2);
+                out |= v << (8 * k);
+            }
+            *reinterpret_cast<uint32_t*>(dstp + rr * L.pitch) = out;
         }
     } else {
 #pragma unroll
-        for (int k = 0; k < 4; k++) {
-            const int px = px0 + k;
-            if (px >= -ORBFE_EDGE && px < L.w + ORBFE_EDGE)
-                out |= resize_px_generic(r0, r1, __ldg(b.tabs + L.tabX + reflect101(px, L.w)), b0, b1) << (8 * k);
+        for (int rr = 0; rr < PYR_ROWS; rr++) {
+            if (row0 + rr >= nrows) break;
+            const uint2 yt = __ldg(b.tabs + L.tabY + reflect101(row0 + rr - ORBFE_EDGE, L.h));
+            const uint8_t* r0 = sint + (uint32_t)((int)yt.x * P.pitch);
+            const uint8_t* r1 = r0 + P.pitch;
+            const int b0 = yt.y & 0xFFFF, b1 = yt.y >> 16;
+            uint32_t out = 0;
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                const int px = px0 + k;
+                if (px >= -ORBFE_EDGE && px < L.w + ORBFE_EDGE)
+                    out |= resize_px_generic(r0, r1, __ldg(b.tabs + L.tabX + reflect101(px, L.w)), b0, b1) << (8 * k);
+            }
+            *reinterpret_cast<uint32_t*>(dstp + rr * L.pitch) = out;
         }
     }
-    *reinterpret_cast<uint32_t*>(slab + (uint32_t)(L.pyrOff + row * L.pitch + g * 4)) = out;
 }
 
 /* --------------------------------------------------------------------------------------------------- blur */
@@ -606,41 +620,48 @@ __global__ void __launch_bounds__(FS_WARPS * 32) k_fast_stream(const __grid_cons
     }
 }
 
-/* One CTA (64 threads) = one cell: scatter the cell's raw corners into a zeroed score tile, keep the strict local maxima
- * (cv::FAST nonmaxSuppression: neighbours outside the cell's candidate area or below the threshold count as 0), write
- * them in (y, x) order.  A cell that ends up empty is queued for the minTh fallback (k_fast_cells_list). */
-#define FN_NT 64
+/* One warp = one cell (four cells per CTA, no block barrier): scatter the cell's raw corners into a zeroed score tile,
+ * keep the strict local maxima (cv::FAST nonmaxSuppression: neighbours outside the cell's candidate area or below the
+ * threshold count as 0), write them in (y, x) order.  A cell that ends up empty is queued for the minTh fallback
+ * (k_fast_cells_list). */
+#define FN_WARPS 4
 #define FN_TP 72
-__global__ void __launch_bounds__(FN_NT) k_fast_nms(const __grid_constant__ ExDesc d, ExBuffers b) {
-    __shared__ __align__(16) uint8_t s_sc[FN_TP * FN_TP];
-    __shared__ uint32_t s_mask[(FAST_LISTCAP + 31) / 32 + 1];
-    const int cellIdx = blockIdx.x;
+__global__ void __launch_bounds__(FN_WARPS * 32) k_fast_nms(const __grid_constant__ ExDesc d, ExBuffers b) {
+    __shared__ __align__(16) uint8_t s_scAll[FN_WARPS][FN_TP * 80];   /* (ch+2) rows x tp <= 72 x 80 */
+    __shared__ uint32_t s_maskAll[FN_WARPS][(FAST_LISTCAP + 31) / 32 + 1];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int cellIdx = blockIdx.x * FN_WARPS + warp;
+    if (cellIdx >= d.nCells) return;
     const size_t f = blockIdx.y;
+    uint8_t* s_sc = s_scAll[warp];
+    uint32_t* s_mask = s_maskAll[warp];
     const CellDesc cell = b.cells[cellIdx];
     int* countOut = b.cellCount + f * d.nCells + cellIdx;
     const int cw = cell.rw - 6, ch = cell.rh - 6;
     if (cw <= 0 || ch <= 0) {
-        if (threadIdx.x == 0) *countOut = 0;
+        if (lane == 0) *countOut = 0;
         return;
     }
     int* rawCountP = b.rawCount + f * d.nCells + cellIdx;
     const int n = *rawCountP;
-    const LevelDesc& L = d.lv[cell.level];
-    const uint32_t* raw = b.raw + f * (size_t)d.rawCap + L.rawBase + (cellIdx - L.cellBase) * L.rawStride;
     int total = 0;
     if (n > 0) {
-        const int tp = (cw + 2 + 7) & ~7, nwords = (cw * ch + 31) >> 5;
-        for (int i = threadIdx.x; i < (ch + 2) * tp / 8; i += FN_NT) reinterpret_cast<uint2*>(s_sc)[i] = make_uint2(0, 0);
-        for (int i = threadIdx.x; i < nwords; i += FN_NT) s_mask[i] = 0;
-        __syncthreads();
+        const LevelDesc& L = d.lv[cell.level];
+        const uint32_t* raw = b.raw + f * (size_t)d.rawCap + L.rawBase + (cellIdx - L.cellBase) * L.rawStride;
+        const int tp = (cw + 2 + 15) & ~15, nwords = (cw * ch + 31) >> 5;
+        /* the first raw entries are fetched while the tile is being cleared */
+        uint32_t e0 = lane < n ? __ldg(raw + lane) : 0u, e1 = lane + 32 < n ? __ldg(raw + lane + 32) : 0u;
+        for (int i = lane; i < (ch + 2) * tp / 16; i += 32) reinterpret_cast<uint4*>(s_sc)[i] = make_uint4(0, 0, 0, 0);
+        for (int i = lane; i < nwords; i += 32) s_mask[i] = 0;
+        __syncwarp();
         const int bx = 3 + cell.xoff - 1, by = 3 + cell.yoff - 1; /* raw x,y are relative to the 16 px border; tile has a 1 px apron */
-        for (int e = threadIdx.x; e < n; e += FN_NT) {
-            const uint32_t p = raw[e];
+        for (int e = lane; e < n; e += 32) {
+            const uint32_t p = e < 32 ? e0 : (e < 64 ? e1 : __ldg(raw + e));
             s_sc[(int)(((p >> 12) & 0xFFF) - by) * tp + (int)((p & 0xFFF) - bx)] = (uint8_t)(p >> 24);
         }
-        __syncthreads();
-        for (int e = threadIdx.x; e < n; e += FN_NT) {
-            const uint32_t p = raw[e];
+        __syncwarp();
+        for (int e = lane; e < n; e += 32) {
+            const uint32_t p = e < 32 ? e0 : (e < 64 ? e1 : __ldg(raw + e));
             const int px = (int)(p & 0xFFF) - bx, py = (int)((p >> 12) & 0xFFF) - by;   /* 1-based inside the tile */
             const uint8_t* sc = s_sc + py * tp + px;
             const int v = sc[0];
@@ -651,38 +672,36 @@ __global__ void __launch_bounds__(FN_NT) k_fast_nms(const __grid_constant__ ExDe
                 atomicOr(&s_mask[pi >> 5], 1u << (pi & 31));
             }
         }
-        __syncthreads();
-        if (threadIdx.x < 32) {
-            /* ordered output by one warp: lane owns a contiguous run of mask words */
-            const int lane = threadIdx.x, per = (nwords + 31) >> 5;
-            const int wbeg = min(lane * per, nwords), wend = min(wbeg + per, nwords);
-            int mine = 0;
-            for (int i = wbeg; i < wend; i++) mine += __popc(s_mask[i]);
-            int incl = mine;
+        __syncwarp();
+        /* ordered output: lane owns a contiguous run of mask words */
+        const int per = (nwords + 31) >> 5;
+        const int wbeg = min(lane * per, nwords), wend = min(wbeg + per, nwords);
+        int mine = 0;
+        for (int i = wbeg; i < wend; i++) mine += __popc(s_mask[i]);
+        int incl = mine;
 #pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                const int t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
-                if (lane >= o) incl += t;
-            }
-            total = __shfl_sync(0xFFFFFFFFu, incl, 31);
-            int k = incl - mine;
-            uint32_t* out = b.cand + f * d.candCap + cell.candBase;
-            const uint32_t invcw = cell.invcw;
-            for (int i = wbeg; i < wend; i++) {
-                uint32_t mm = s_mask[i];
-                while (mm) {
-                    const int bit = __ffs(mm) - 1;
-                    mm &= mm - 1;
-                    const int pi = i * 32 + bit;
-                    const int py = (int)(((uint32_t)pi * invcw) >> 24), px = pi - py * cw;
-                    out[k++] = (uint32_t)(px + 3 + cell.xoff) | ((uint32_t)(py + 3 + cell.yoff) << 12) | ((uint32_t)s_sc[(py + 1) * tp + px + 1] << 24);
-                }
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+            if (lane >= o) incl += t;
+        }
+        total = __shfl_sync(0xFFFFFFFFu, incl, 31);
+        int k = incl - mine;
+        uint32_t* out = b.cand + f * d.candCap + cell.candBase;
+        const uint32_t invcw = cell.invcw;
+        for (int i = wbeg; i < wend; i++) {
+            uint32_t mm = s_mask[i];
+            while (mm) {
+                const int bit = __ffs(mm) - 1;
+                mm &= mm - 1;
+                const int pi = i * 32 + bit;
+                const int py = (int)(((uint32_t)pi * invcw) >> 24), px = pi - py * cw;
+                out[k++] = (uint32_t)(px + 3 + cell.xoff) | ((uint32_t)(py + 3 + cell.yoff) << 12) | ((uint32_t)s_sc[(py + 1) * tp + px + 1] << 24);
             }
         }
     }
-    if (threadIdx.x == 0) {
+    if (lane == 0) {
         *countOut = total;
-        *rawCountP = 0;                                   /* ready for the next batch */
+        if (n > 0) *rawCountP = 0;                        /* ready for the next batch */
         if (total == 0) b.fbList[atomicAdd(b.fbCount, 1)] = (int)f * d.nCells + cellIdx;
     }
 }
@@ -1202,11 +1221,11 @@ int orbfe_launch_extract(orbfe_extractor* ex, const uint8_t* d_images, int nfram
     for (int l = 1; l < d.nlevels; l++) {
         const LevelDesc& L = d.lv[l];
         const int nInt = L.w >> 2, intWarps = (nInt + 31) / 32;
-        k_pyramid_level<<<dim3(intWarps + 1, (L.h + 2 * ORBFE_EDGE + 7) / 8, nframes), dim3(32, 8), 0, st>>>(d, ex->b, l);
+        k_pyramid_level<<<dim3(intWarps + 1, (L.h + 2 * ORBFE_EDGE + 8 * PYR_ROWS - 1) / (8 * PYR_ROWS), nframes), dim3(32, 8), 0, st>>>(d, ex->b, l);
     }
     STAGE_MARK();
     k_fast_stream<<<dim3((d.nStrips + FS_WARPS - 1) / FS_WARPS, nframes), FS_WARPS * 32, 0, st>>>(d, ex->b);
-    k_fast_nms<<<dim3(d.nCells, nframes), FN_NT, 0, st>>>(d, ex->b);
+    k_fast_nms<<<dim3((d.nCells + FN_WARPS - 1) / FN_WARPS, nframes), FN_WARPS * 32, 0, st>>>(d, ex->b);
     k_fast_cells_list<<<148 * 4, FAST_NT, ex->fastSmem, st>>>(d, ex->b);
     STAGE_MARK();
     for (int l = 0; l < d.nlevels; l++) {
