@@ -511,7 +511,7 @@ __global__ void __launch_bounds__(FAST_NT, 8) k_fast_cells_list(const __grid_con
  * k_fast_nms then does the cell-local non-maximum suppression and ordering. */
 #define FS_BROWS (FS_R + 6)   /* rows yc-3 .. yc+FS_R+2 of the current chunk */
 #define FS_PW 33               /* words per buffered row: 32 + 1 so that equal columns of different rows hit different banks */
-__global__ void __launch_bounds__(FS_WARPS * 32) k_fast_stream(const __grid_constant__ ExDesc d, ExBuffers b) {
+__global__ void __launch_bounds__(FS_WARPS * 32, 10) k_fast_stream(const __grid_constant__ ExDesc d, ExBuffers b) {
     __shared__ __align__(16) uint32_t s_buf[FS_WARPS][FS_BROWS][FS_PW];
     __shared__ uint32_t s_hits[FS_WARPS][FS_R][32];
     __shared__ uint16_t s_q[FS_WARPS][FS_R * FS_COLS + 32];
@@ -1127,13 +1127,18 @@ __global__ void __launch_bounds__(OD_NT) k_orient_describe(const __grid_constant
     const int pitch = L.pitch;
     const uint8_t* p = b.pyr + f * d.pyrSlab + (uint32_t)(L.pyrOff + (y + ORBFE_EDGE - 15) * pitch + ORBFE_ROW_LEAD + x + u);
     const uint32_t rows = c_rowmask[lane];
+    /* all 31 rows are fetched unconditionally (the 31 x 32 box around a keypoint is always inside the padded level), so
+     * the loads go out back to back; rows outside the disc are masked afterwards */
+    int pv[31];
+#pragma unroll
+    for (int v = 0; v < 31; v++) pv[v] = __ldg(p + v * pitch);
+    asm volatile("" ::: "memory");   /* keep the 31 loads ahead of their uses: one memory round trip, not 31 */
     int colsum = 0, m01 = 0;
 #pragma unroll
-    for (int v = -15; v <= 15; v++, p += pitch) {
-        int val = 0;
-        if (rows & (1u << (v + 15))) val = *p;
+    for (int v = 0; v < 31; v++) {
+        const int val = (rows >> v) & 1u ? pv[v] : 0;
         colsum += val;
-        m01 += v * val;
+        m01 += (v - 15) * val;
     }
     int m10 = u * colsum;
 #pragma unroll
@@ -1152,11 +1157,11 @@ __global__ void __launch_bounds__(OD_NT) k_orient_describe(const __grid_constant
     const float ca = (float)cd, sa = (float)sd;
     const int bpitch = L.bpitch;
     const uint8_t* cb = b.blur + f * d.blurSlab + (uint32_t)(L.blurOff + y * bpitch + x);
-    const float4* pt = reinterpret_cast<const float4*>(s_pat) + 8 * lane;
+    const float4* pt = reinterpret_cast<const float4*>(s_pat) + lane;   /* [test pair k][lane]: conflict-free */
     int off[16];
 #pragma unroll
     for (int k = 0; k < 8; k++) {
-        const float4 t = pt[k]; /* x0, y0, x1, y1 */
+        const float4 t = pt[32 * k]; /* x0, y0, x1, y1 of tests 16*lane + 2k, 2k+1 */
         const int r0 = __float2int_rn(__fadd_rn(__fmul_rn(t.x, sa), __fmul_rn(t.y, ca)));
         const int q0 = __float2int_rn(__fsub_rn(__fmul_rn(t.x, ca), __fmul_rn(t.y, sa)));
         const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(t.z, sa), __fmul_rn(t.w, ca)));
@@ -1166,7 +1171,8 @@ __global__ void __launch_bounds__(OD_NT) k_orient_describe(const __grid_constant
     }
     int tv[16];
 #pragma unroll
-    for (int k = 0; k < 16; k++) tv[k] = cb[off[k]];   /* 16 independent gathers in flight */
+    for (int k = 0; k < 16; k++) tv[k] = __ldg(cb + off[k]);   /* 16 independent gathers in flight */
+    asm volatile("" ::: "memory");
     uint32_t val = 0;
 #pragma unroll
     for (int k = 0; k < 8; k++) val |= (uint32_t)(tv[2 * k] < tv[2 * k + 1]) << k;
@@ -1176,8 +1182,10 @@ __global__ void __launch_bounds__(OD_NT) k_orient_describe(const __grid_constant
 
 /* --------------------------------------------------------------------------------------------- host driver */
 int orbfe_upload_constants(const int* umax16, const int8_t* pattern1024) {
-    float pf[1024];
-    for (int i = 0; i < 1024; i++) pf[i] = (float)pattern1024[i];
+    float pf[1024];   /* device layout [k = 0..7][lane = 0..31][x0,y0,x1,y1]: descriptor byte `lane`, bit k */
+    for (int lane = 0; lane < 32; lane++)
+        for (int k = 0; k < 8; k++)
+            for (int c = 0; c < 4; c++) pf[(k * 32 + lane) * 4 + c] = (float)pattern1024[(lane * 8 + k) * 4 + c];
     uint32_t rowmask[32];
     for (int lane = 0; lane < 32; lane++) {
         const int u = lane - 15, au = u < 0 ? -u : u;
