@@ -73,17 +73,28 @@ static __device__ __forceinline__ uint32_t resize_px_generic(const uint8_t* r0, 
     return (uint32_t)((((b0 * (h0 >> 4)) >> 16) + ((b1 * (h1 >> 4)) >> 16) + 2) >> 2);
 }
 
-#define PYR_ROWS 2   /* output rows per thread: the horizontal tables, selectors and shifts are shared between them */
-__global__ void __launch_bounds__(256) k_pyramid_level(const __grid_constant__ ExDesc d, ExBuffers b, int level) {
+#define PYR_ROWS 4   /* output rows per thread: the horizontal tables, selectors and shifts are shared between them */
+/* Geometry of one resize launch, passed by value so that every field sits at a fixed constant-bank address. */
+struct ResizeArgs {
+    int w, h, pitch, pyrOff;      /* destination level */
+    int spitch, spyrOff;          /* source level */
+    int tabX, tabY;
+};
+
+/* vertical blend of OpenCV's fixed-point bilinear: (((b0*(h0>>4))>>16) + ((b1*(h1>>4))>>16) + 2) >> 2, with the
+ * >>16 taken as the high half of a product by b<<16 */
+static __device__ __forceinline__ uint32_t resize_vblend(uint32_t h0, uint32_t h1, uint32_t b0s, uint32_t b1s) {
+    return (__umulhi(h0 >> 4, b0s) + __umulhi(h1 >> 4, b1s) + 2u) >> 2;
+}
+
+__global__ void __launch_bounds__(256) k_pyramid_level(const __grid_constant__ ExDesc d, ExBuffers b, const __grid_constant__ ResizeArgs a) {
     /* block = 32 x 8: a warp works on PYR_ROWS consecutive output rows.  Warps [0, nInteriorWarps) take the groups that
      * lie fully inside the image (fast path, no divergence); the last warp takes every group that touches the border. */
-    const LevelDesc& L = d.lv[level];
-    const LevelDesc& P = d.lv[level - 1];
-    const int nrows = L.h + 2 * ORBFE_EDGE;
+    const int nrows = a.h + 2 * ORBFE_EDGE;
     const int row0 = (blockIdx.y * 8 + threadIdx.y) * PYR_ROWS;
     if (row0 >= nrows) return;
-    const int groups = L.pitch >> 2;
-    const int gFirst = ORBFE_ROW_LEAD / 4, nInt = L.w >> 2;     /* interior groups: px0 = 0, 4, ... */
+    const int groups = a.pitch >> 2;
+    const int gFirst = ORBFE_ROW_LEAD / 4, nInt = a.w >> 2;     /* interior groups: px0 = 0, 4, ... */
     const int tx = blockIdx.x * 32 + threadIdx.x;
     const int intThreads = (nInt + 31) & ~31;
     int g;
@@ -98,56 +109,60 @@ __global__ void __launch_bounds__(256) k_pyramid_level(const __grid_constant__ E
         if (g >= groups) return;
         interior = false;
     }
-    const size_t f = blockIdx.z;
-    uint8_t* slab = b.pyr + f * d.pyrSlab;
-    const uint8_t* sint = slab + (uint32_t)(P.pyrOff + ORBFE_EDGE * P.pitch + ORBFE_ROW_LEAD);
+    uint8_t* slab = b.pyr + (size_t)blockIdx.z * d.pyrSlab;
+    const uint8_t* sint = slab + (uint32_t)(a.spyrOff + ORBFE_EDGE * a.spitch + ORBFE_ROW_LEAD);
     const int px0 = g * 4 - ORBFE_ROW_LEAD;
-    uint8_t* dstp = slab + (uint32_t)(L.pyrOff + row0 * L.pitch + g * 4);
+    uint8_t* dstp = slab + (uint32_t)(a.pyrOff + row0 * a.pitch + g * 4);
+    const uint2* tabY = b.tabs + a.tabY;
     if (interior) {
-        const uint4* tp = reinterpret_cast<const uint4*>(b.tabs + L.tabX + px0); /* tabX is 4-entry aligned */
+        const uint4* tp = reinterpret_cast<const uint4*>(b.tabs + a.tabX + px0); /* tabX is 4-entry aligned */
         const uint4 ta = __ldg(tp), tb = __ldg(tp + 1); /* entries (sx, c0|c1<<16) of the four pixels */
+        uint2 yt[PYR_ROWS];
+#pragma unroll
+        for (int rr = 0; rr < PYR_ROWS; rr++) yt[rr] = __ldg(tabY + reflect101(min(row0 + rr, nrows - 1) - ORBFE_EDGE, a.h));
         const uint32_t sx0 = ta.x;
         const uint32_t base = sx0 & ~3u, sh = (sx0 & 3u) * 8;
         const uint32_t cfs[4] = {ta.y, ta.w, tb.y, tb.w};
         /* byte selectors (off, off+1) -> low half; off = sx - sx0 in 0..6 (host-checked): four taps within 8 bytes */
         const uint32_t sel[4] = {0x10u, (ta.z - sx0) * 0x11u + 0x10u, (tb.x - sx0) * 0x11u + 0x10u, (tb.z - sx0) * 0x11u + 0x10u};
+        uint32_t wsrc[PYR_ROWS][6];   /* all source words of all rows are requested before the arithmetic starts */
+#pragma unroll
+        for (int rr = 0; rr < PYR_ROWS; rr++) {
+            /* row yt.x+1 and column sx+1 may be the source's own border: their coefficient is then 0 */
+            const uint32_t* q0 = reinterpret_cast<const uint32_t*>(sint + (uint32_t)((int)yt[rr].x * a.spitch) + base);
+            const uint32_t* q1 = reinterpret_cast<const uint32_t*>(reinterpret_cast<const uint8_t*>(q0) + a.spitch);
+            wsrc[rr][0] = q0[0]; wsrc[rr][1] = q0[1]; wsrc[rr][2] = q0[2];
+            wsrc[rr][3] = q1[0]; wsrc[rr][4] = q1[1]; wsrc[rr][5] = q1[2];
+        }
+        asm volatile("" ::: "memory");
 #pragma unroll
         for (int rr = 0; rr < PYR_ROWS; rr++) {
             if (row0 + rr >= nrows) break;
-            const uint2 yt = __ldg(b.tabs + L.tabY + reflect101(row0 + rr - ORBFE_EDGE, L.h));
-            /* row yt.x+1 and column sx+1 may be the source's own border: their coefficient is then 0 */
-            const uint32_t* q0 = reinterpret_cast<const uint32_t*>(sint + (uint32_t)((int)yt.x * P.pitch) + base);
-            const uint32_t* q1 = reinterpret_cast<const uint32_t*>(reinterpret_cast<const uint8_t*>(q0) + P.pitch);
-            const int b0 = yt.y & 0xFFFF, b1 = yt.y >> 16;
-            const uint32_t a0 = q0[0], a1 = q0[1], a2 = q0[2], c0w = q1[0], c1w = q1[1], c2w = q1[2];
-            const uint32_t u0 = __funnelshift_r(a0, a1, sh), u1 = __funnelshift_r(a1, a2, sh); /* bytes sx0 .. sx0+7 of row 0 */
-            const uint32_t v0 = __funnelshift_r(c0w, c1w, sh), v1 = __funnelshift_r(c1w, c2w, sh);
-            uint32_t out = 0;
+            const uint32_t b0s = (yt[rr].y & 0xFFFFu) << 16, b1s = yt[rr].y & 0xFFFF0000u;
+            const uint32_t u0 = __funnelshift_r(wsrc[rr][0], wsrc[rr][1], sh), u1 = __funnelshift_r(wsrc[rr][1], wsrc[rr][2], sh); /* bytes sx0 .. sx0+7 */
+            const uint32_t v0 = __funnelshift_r(wsrc[rr][3], wsrc[rr][4], sh), v1 = __funnelshift_r(wsrc[rr][4], wsrc[rr][5], sh);
+            uint32_t o[4];
 #pragma unroll
-            for (int k = 0; k < 4; k++) {
-                const uint32_t h0 = __dp2a_lo(cfs[k], __byte_perm(u0, u1, sel[k]), 0u);
-                const uint32_t h1 = __dp2a_lo(cfs[k], __byte_perm(v0, v1, sel[k]), 0u);
-                const uint32_t v = (uint32_t)((((b0 * (int)(h0 >> 4)) >> 16) + ((b1 * (int)(h1 >> 4)) >> 16) + 2) >> 2);
-                out |= v << (8 * k);
-            }
-            *reinterpret_cast<uint32_t*>(dstp + rr * L.pitch) = out;
+            for (int k = 0; k < 4; k++)
+                o[k] = resize_vblend(__dp2a_lo(cfs[k], __byte_perm(u0, u1, sel[k]), 0u), __dp2a_lo(cfs[k], __byte_perm(v0, v1, sel[k]), 0u), b0s, b1s);
+            *reinterpret_cast<uint32_t*>(dstp + rr * a.pitch) = __byte_perm(__byte_perm(o[0], o[1], 0x0040), __byte_perm(o[2], o[3], 0x0040), 0x5410);
         }
     } else {
 #pragma unroll
         for (int rr = 0; rr < PYR_ROWS; rr++) {
             if (row0 + rr >= nrows) break;
-            const uint2 yt = __ldg(b.tabs + L.tabY + reflect101(row0 + rr - ORBFE_EDGE, L.h));
-            const uint8_t* r0 = sint + (uint32_t)((int)yt.x * P.pitch);
-            const uint8_t* r1 = r0 + P.pitch;
+            const uint2 yt = __ldg(tabY + reflect101(row0 + rr - ORBFE_EDGE, a.h));
+            const uint8_t* r0 = sint + (uint32_t)((int)yt.x * a.spitch);
+            const uint8_t* r1 = r0 + a.spitch;
             const int b0 = yt.y & 0xFFFF, b1 = yt.y >> 16;
             uint32_t out = 0;
 #pragma unroll
             for (int k = 0; k < 4; k++) {
                 const int px = px0 + k;
-                if (px >= -ORBFE_EDGE && px < L.w + ORBFE_EDGE)
-                    out |= resize_px_generic(r0, r1, __ldg(b.tabs + L.tabX + reflect101(px, L.w)), b0, b1) << (8 * k);
+                if (px >= -ORBFE_EDGE && px < a.w + ORBFE_EDGE)
+                    out |= resize_px_generic(r0, r1, __ldg(b.tabs + a.tabX + reflect101(px, a.w)), b0, b1) << (8 * k);
             }
-            *reinterpret_cast<uint32_t*>(dstp + rr * L.pitch) = out;
+            *reinterpret_cast<uint32_t*>(dstp + rr * a.pitch) = out;
         }
     }
 }
@@ -170,23 +185,35 @@ __global__ void __launch_bounds__(256) k_blur7(const __grid_constant__ ExDesc d,
     const uint32_t KLO = 18u | (34u << 8) | (48u << 16) | (56u << 24);  /* taps -3..0 */
     const uint32_t KHI = 48u | (34u << 8) | (18u << 16);                /* taps +1..+3 */
     const int ymax = L.h + ORBFE_EDGE - 1;
-    static_assert(BLUR_PAIRS * (BLUR_TW / 4) % 256 == 0 && BLUR_TW == 64, "horizontal pass assumes whole sweeps of 256 threads");
+    static_assert(BLUR_PAIRS * (BLUR_TW / 4) == 512 && BLUR_TW == 64, "horizontal pass assumes two whole sweeps of 256 threads");
+    {
+        const int q = threadIdx.x & 15;
+        uint32_t w[2][2][3];   /* [sweep][row of the pair][word]: all twelve loads are issued before any is used */
 #pragma unroll
-    for (int sweep = 0; sweep < BLUR_PAIRS * (BLUR_TW / 4) / 256; sweep++) {
-        const int j = (threadIdx.x >> 4) + 16 * sweep, q = threadIdx.x & 15; /* row pair j, pixel group q (4 px) */
-        uint32_t hrow[2][4];
+        for (int sweep = 0; sweep < 2; sweep++)
 #pragma unroll
-        for (int rr = 0; rr < 2; rr++) {
-            const int gy = min(y0 - 4 + 2 * j + rr, ymax);
-            const uint32_t* p = reinterpret_cast<const uint32_t*>(pad + (uint32_t)((gy + ORBFE_EDGE) * L.pitch + 4 * q));
-            const uint32_t w0 = __ldg(p), w1 = __ldg(p + 1), w2 = __ldg(p + 2);   /* px x-4..x-1 | x..x+3 | x+4..x+7 */
-            hrow[rr][0] = __dp4a(__funnelshift_r(w0, w1, 8), KLO, __dp4a(__funnelshift_r(w1, w2, 8), KHI, 0u));
-            hrow[rr][1] = __dp4a(__funnelshift_r(w0, w1, 16), KLO, __dp4a(__funnelshift_r(w1, w2, 16), KHI, 0u));
-            hrow[rr][2] = __dp4a(__funnelshift_r(w0, w1, 24), KLO, __dp4a(__funnelshift_r(w1, w2, 24), KHI, 0u));
-            hrow[rr][3] = __dp4a(w1, KLO, __dp4a(w2, KHI, 0u));
+            for (int rr = 0; rr < 2; rr++) {
+                const int j = (threadIdx.x >> 4) + 16 * sweep;
+                const int gy = min(y0 - 4 + 2 * j + rr, ymax);
+                const uint32_t* p = reinterpret_cast<const uint32_t*>(pad + (uint32_t)((gy + ORBFE_EDGE) * L.pitch + 4 * q));
+                w[sweep][rr][0] = __ldg(p); w[sweep][rr][1] = __ldg(p + 1); w[sweep][rr][2] = __ldg(p + 2);   /* px x-4..x-1 | x..x+3 | x+4..x+7 */
+            }
+        asm volatile("" ::: "memory");
+#pragma unroll
+        for (int sweep = 0; sweep < 2; sweep++) {
+            const int j = (threadIdx.x >> 4) + 16 * sweep;   /* row pair j, pixel group q (4 px) */
+            uint32_t hrow[2][4];
+#pragma unroll
+            for (int rr = 0; rr < 2; rr++) {
+                const uint32_t w0 = w[sweep][rr][0], w1 = w[sweep][rr][1], w2 = w[sweep][rr][2];
+                hrow[rr][0] = __dp4a(__funnelshift_r(w0, w1, 8), KLO, __dp4a(__funnelshift_r(w1, w2, 8), KHI, 0u));
+                hrow[rr][1] = __dp4a(__funnelshift_r(w0, w1, 16), KLO, __dp4a(__funnelshift_r(w1, w2, 16), KHI, 0u));
+                hrow[rr][2] = __dp4a(__funnelshift_r(w0, w1, 24), KLO, __dp4a(__funnelshift_r(w1, w2, 24), KHI, 0u));
+                hrow[rr][3] = __dp4a(w1, KLO, __dp4a(w2, KHI, 0u));
+            }
+            *reinterpret_cast<uint4*>(&s_h[j][4 * q]) = make_uint4(hrow[0][0] | (hrow[1][0] << 16), hrow[0][1] | (hrow[1][1] << 16),
+                                                                   hrow[0][2] | (hrow[1][2] << 16), hrow[0][3] | (hrow[1][3] << 16));
         }
-        *reinterpret_cast<uint4*>(&s_h[j][4 * q]) = make_uint4(hrow[0][0] | (hrow[1][0] << 16), hrow[0][1] | (hrow[1][1] << 16),
-                                                               hrow[0][2] | (hrow[1][2] << 16), hrow[0][3] | (hrow[1][3] << 16));
     }
     __syncthreads();
     uint8_t* dst = b.blur + f * d.blurSlab + L.blurOff;
@@ -511,7 +538,7 @@ __global__ void __launch_bounds__(FAST_NT, 8) k_fast_cells_list(const __grid_con
  * k_fast_nms then does the cell-local non-maximum suppression and ordering. */
 #define FS_BROWS (FS_R + 6)   /* rows yc-3 .. yc+FS_R+2 of the current chunk */
 #define FS_PW 33               /* words per buffered row: 32 + 1 so that equal columns of different rows hit different banks */
-__global__ void __launch_bounds__(FS_WARPS * 32, 10) k_fast_stream(const __grid_constant__ ExDesc d, ExBuffers b) {
+__global__ void __launch_bounds__(FS_WARPS * 32, 8) k_fast_stream(const __grid_constant__ ExDesc d, ExBuffers b) {
     __shared__ __align__(16) uint32_t s_buf[FS_WARPS][FS_BROWS][FS_PW];
     __shared__ uint32_t s_hits[FS_WARPS][FS_R][32];
     __shared__ uint16_t s_q[FS_WARPS][FS_R * FS_COLS + 32];
@@ -540,12 +567,16 @@ __global__ void __launch_bounds__(FS_WARPS * 32, 10) k_fast_stream(const __grid_
     const uint32_t k127mt = (uint32_t)(127 - th) * 0x01010101u;
     int* rawCount = b.rawCount + f * d.nCells;
     uint32_t* raw = b.raw + f * (size_t)d.rawCap;
+    /* the fetch of the next row is always one step ahead of its use (rows beyond the strip stay inside the padded level) */
+    uint32_t nxt = __ldg(reinterpret_cast<const uint32_t*>(p));
     for (int c0 = 0; c0 < nrows; c0 += FS_R) {
         const int rows = min(FS_R, nrows - c0);
         __syncwarp();
-        /* 1. sieve, one row per step: buffer rows r (y-3), r+3 (y), r+6 (y+3, fetched now) */
-        for (int r = 0; r < rows; r++, p += pitch) {
-            const uint32_t top = __ldg(reinterpret_cast<const uint32_t*>(p));
+        /* 1. sieve, one row per step: buffer rows r (y-3), r+3 (y), r+6 (y+3, fetched one step earlier) */
+        for (int r = 0; r < rows; r++) {
+            const uint32_t top = nxt;
+            p += pitch;
+            nxt = __ldg(reinterpret_cast<const uint32_t*>(p));
             buf[(r + 6) * FS_PW + lane] = top;
             const uint32_t cen = buf[(r + 3) * FS_PW + lane], bot = buf[r * FS_PW + lane];
             const uint32_t lw = __shfl_up_sync(0xFFFFFFFFu, cen, 1), rw = __shfl_down_sync(0xFFFFFFFFu, cen, 1);
@@ -1229,7 +1260,8 @@ int orbfe_launch_extract(orbfe_extractor* ex, const uint8_t* d_images, int nfram
     for (int l = 1; l < d.nlevels; l++) {
         const LevelDesc& L = d.lv[l];
         const int nInt = L.w >> 2, intWarps = (nInt + 31) / 32;
-        k_pyramid_level<<<dim3(intWarps + 1, (L.h + 2 * ORBFE_EDGE + 8 * PYR_ROWS - 1) / (8 * PYR_ROWS), nframes), dim3(32, 8), 0, st>>>(d, ex->b, l);
+        k_pyramid_level<<<dim3(intWarps + 1, (L.h + 2 * ORBFE_EDGE + 8 * PYR_ROWS - 1) / (8 * PYR_ROWS), nframes), dim3(32, 8), 0, st>>>(
+            d, ex->b, ResizeArgs{L.w, L.h, L.pitch, L.pyrOff, d.lv[l - 1].pitch, d.lv[l - 1].pyrOff, L.tabX, L.tabY});
     }
     STAGE_MARK();
     k_fast_stream<<<dim3((d.nStrips + FS_WARPS - 1) / FS_WARPS, nframes), FS_WARPS * 32, 0, st>>>(d, ex->b);
