@@ -88,83 +88,95 @@ static __device__ __forceinline__ uint32_t resize_vblend(uint32_t h0, uint32_t h
 }
 
 __global__ void __launch_bounds__(256) k_pyramid_level(const __grid_constant__ ExDesc d, ExBuffers b, const __grid_constant__ ResizeArgs a) {
-    /* block = 32 x 8: a warp works on PYR_ROWS consecutive output rows.  Warps [0, nInteriorWarps) take the groups that
-     * lie fully inside the image (fast path, no divergence); the last warp takes every group that touches the border. */
-    const int nrows = a.h + 2 * ORBFE_EDGE;
-    const int row0 = (blockIdx.y * 8 + threadIdx.y) * PYR_ROWS;
-    if (row0 >= nrows) return;
-    const int groups = a.pitch >> 2;
-    const int gFirst = ORBFE_ROW_LEAD / 4, nInt = a.w >> 2;     /* interior groups: px0 = 0, 4, ... */
+    /* block = 32 x 8: a warp works on PYR_ROWS consecutive interior rows; a thread on one group of four pixels that
+     * lies fully inside the image.  The 19 px border (and the last 1-3 columns when w % 4 != 0) is filled afterwards for
+     * all levels at once by k_pyramid_borders: the next level's resize never reads a border pixel with a non-zero weight. */
+    const int row0 = (blockIdx.y * 8 + threadIdx.y) * PYR_ROWS;   /* interior row */
+    if (row0 >= a.h) return;
     const int tx = blockIdx.x * 32 + threadIdx.x;
-    const int intThreads = (nInt + 31) & ~31;
-    int g;
-    bool interior;
-    if (tx < intThreads) {
-        if (tx >= nInt) return;
-        g = gFirst + tx;
-        interior = true;
-    } else {
-        const int j = tx - intThreads;                          /* border groups: [0, gFirst) then [gFirst+nInt, groups) */
-        g = j < gFirst ? j : gFirst + nInt + (j - gFirst);
-        if (g >= groups) return;
-        interior = false;
-    }
+    if (tx > (a.w >> 2)) return;
     uint8_t* slab = b.pyr + (size_t)blockIdx.z * d.pyrSlab;
     const uint8_t* sint = slab + (uint32_t)(a.spyrOff + ORBFE_EDGE * a.spitch + ORBFE_ROW_LEAD);
-    const int px0 = g * 4 - ORBFE_ROW_LEAD;
-    uint8_t* dstp = slab + (uint32_t)(a.pyrOff + row0 * a.pitch + g * 4);
+    const int px0 = tx * 4;
+    uint8_t* dstp = slab + (uint32_t)(a.pyrOff + (row0 + ORBFE_EDGE) * a.pitch + ORBFE_ROW_LEAD + px0);
     const uint2* tabY = b.tabs + a.tabY;
-    if (interior) {
-        const uint4* tp = reinterpret_cast<const uint4*>(b.tabs + a.tabX + px0); /* tabX is 4-entry aligned */
-        const uint4 ta = __ldg(tp), tb = __ldg(tp + 1); /* entries (sx, c0|c1<<16) of the four pixels */
-        uint2 yt[PYR_ROWS];
-#pragma unroll
-        for (int rr = 0; rr < PYR_ROWS; rr++) yt[rr] = __ldg(tabY + reflect101(min(row0 + rr, nrows - 1) - ORBFE_EDGE, a.h));
-        const uint32_t sx0 = ta.x;
-        const uint32_t base = sx0 & ~3u, sh = (sx0 & 3u) * 8;
-        const uint32_t cfs[4] = {ta.y, ta.w, tb.y, tb.w};
-        /* byte selectors (off, off+1) -> low half; off = sx - sx0 in 0..6 (host-checked): four taps within 8 bytes */
-        const uint32_t sel[4] = {0x10u, (ta.z - sx0) * 0x11u + 0x10u, (tb.x - sx0) * 0x11u + 0x10u, (tb.z - sx0) * 0x11u + 0x10u};
-        uint32_t wsrc[PYR_ROWS][6];   /* all source words of all rows are requested before the arithmetic starts */
-#pragma unroll
-        for (int rr = 0; rr < PYR_ROWS; rr++) {
-            /* row yt.x+1 and column sx+1 may be the source's own border: their coefficient is then 0 */
-            const uint32_t* q0 = reinterpret_cast<const uint32_t*>(sint + (uint32_t)((int)yt[rr].x * a.spitch) + base);
-            const uint32_t* q1 = reinterpret_cast<const uint32_t*>(reinterpret_cast<const uint8_t*>(q0) + a.spitch);
-            wsrc[rr][0] = q0[0]; wsrc[rr][1] = q0[1]; wsrc[rr][2] = q0[2];
-            wsrc[rr][3] = q1[0]; wsrc[rr][4] = q1[1]; wsrc[rr][5] = q1[2];
-        }
-        asm volatile("" ::: "memory");
-#pragma unroll
-        for (int rr = 0; rr < PYR_ROWS; rr++) {
-            if (row0 + rr >= nrows) break;
-            const uint32_t b0s = (yt[rr].y & 0xFFFFu) << 16, b1s = yt[rr].y & 0xFFFF0000u;
-            const uint32_t u0 = __funnelshift_r(wsrc[rr][0], wsrc[rr][1], sh), u1 = __funnelshift_r(wsrc[rr][1], wsrc[rr][2], sh); /* bytes sx0 .. sx0+7 */
-            const uint32_t v0 = __funnelshift_r(wsrc[rr][3], wsrc[rr][4], sh), v1 = __funnelshift_r(wsrc[rr][4], wsrc[rr][5], sh);
-            uint32_t o[4];
-#pragma unroll
-            for (int k = 0; k < 4; k++)
-                o[k] = resize_vblend(__dp2a_lo(cfs[k], __byte_perm(u0, u1, sel[k]), 0u), __dp2a_lo(cfs[k], __byte_perm(v0, v1, sel[k]), 0u), b0s, b1s);
-            *reinterpret_cast<uint32_t*>(dstp + rr * a.pitch) = __byte_perm(__byte_perm(o[0], o[1], 0x0040), __byte_perm(o[2], o[3], 0x0040), 0x5410);
-        }
-    } else {
-#pragma unroll
-        for (int rr = 0; rr < PYR_ROWS; rr++) {
-            if (row0 + rr >= nrows) break;
-            const uint2 yt = __ldg(tabY + reflect101(row0 + rr - ORBFE_EDGE, a.h));
+    if (tx == (a.w >> 2)) {
+        /* the last 1-3 columns when w % 4 != 0: one lane per row block, byte by byte */
+        for (int rr = 0; rr < PYR_ROWS && row0 + rr < a.h; rr++) {
+            const uint2 yt = __ldg(tabY + row0 + rr);
             const uint8_t* r0 = sint + (uint32_t)((int)yt.x * a.spitch);
-            const uint8_t* r1 = r0 + a.spitch;
-            const int b0 = yt.y & 0xFFFF, b1 = yt.y >> 16;
-            uint32_t out = 0;
-#pragma unroll
-            for (int k = 0; k < 4; k++) {
-                const int px = px0 + k;
-                if (px >= -ORBFE_EDGE && px < a.w + ORBFE_EDGE)
-                    out |= resize_px_generic(r0, r1, __ldg(b.tabs + a.tabX + reflect101(px, a.w)), b0, b1) << (8 * k);
-            }
-            *reinterpret_cast<uint32_t*>(dstp + rr * a.pitch) = out;
+            for (int px = px0; px < a.w; px++)
+                dstp[rr * a.pitch + px - px0] = (uint8_t)resize_px_generic(r0, r0 + a.spitch, __ldg(b.tabs + a.tabX + px), yt.y & 0xFFFF, yt.y >> 16);
         }
+        return;
     }
+    const uint4* tp = reinterpret_cast<const uint4*>(b.tabs + a.tabX + px0); /* tabX is 4-entry aligned */
+    const uint4 ta = __ldg(tp), tb = __ldg(tp + 1); /* entries (sx, c0|c1<<16) of the four pixels */
+    uint2 yt[PYR_ROWS];
+#pragma unroll
+    for (int rr = 0; rr < PYR_ROWS; rr++) yt[rr] = __ldg(tabY + min(row0 + rr, a.h - 1));
+    const uint32_t sx0 = ta.x;
+    const uint32_t base = sx0 & ~3u, sh = (sx0 & 3u) * 8;
+    const uint32_t cfs[4] = {ta.y, ta.w, tb.y, tb.w};
+    /* byte selectors (off, off+1) -> low half; off = sx - sx0 in 0..6 (host-checked): four taps within 8 bytes */
+    const uint32_t sel[4] = {0x10u, (ta.z - sx0) * 0x11u + 0x10u, (tb.x - sx0) * 0x11u + 0x10u, (tb.z - sx0) * 0x11u + 0x10u};
+    uint32_t wsrc[PYR_ROWS][6];   /* all source words of all rows are requested before the arithmetic starts */
+#pragma unroll
+    for (int rr = 0; rr < PYR_ROWS; rr++) {
+        /* row yt.x+1 and column sx+1 may be the source's own border: their coefficient is then 0 */
+        const uint32_t* q0 = reinterpret_cast<const uint32_t*>(sint + (uint32_t)((int)yt[rr].x * a.spitch) + base);
+        const uint32_t* q1 = reinterpret_cast<const uint32_t*>(reinterpret_cast<const uint8_t*>(q0) + a.spitch);
+        wsrc[rr][0] = q0[0]; wsrc[rr][1] = q0[1]; wsrc[rr][2] = q0[2];
+        wsrc[rr][3] = q1[0]; wsrc[rr][4] = q1[1]; wsrc[rr][5] = q1[2];
+    }
+    asm volatile("" ::: "memory");
+#pragma unroll
+    for (int rr = 0; rr < PYR_ROWS; rr++) {
+        if (row0 + rr >= a.h) break;
+        const uint32_t b0s = (yt[rr].y & 0xFFFFu) << 16, b1s = yt[rr].y & 0xFFFF0000u;
+        const uint32_t u0 = __funnelshift_r(wsrc[rr][0], wsrc[rr][1], sh), u1 = __funnelshift_r(wsrc[rr][1], wsrc[rr][2], sh); /* bytes sx0 .. sx0+7 */
+        const uint32_t v0 = __funnelshift_r(wsrc[rr][3], wsrc[rr][4], sh), v1 = __funnelshift_r(wsrc[rr][4], wsrc[rr][5], sh);
+        uint32_t o[4];
+#pragma unroll
+        for (int k = 0; k < 4; k++)
+            o[k] = resize_vblend(__dp2a_lo(cfs[k], __byte_perm(u0, u1, sel[k]), 0u), __dp2a_lo(cfs[k], __byte_perm(v0, v1, sel[k]), 0u), b0s, b1s);
+        *reinterpret_cast<uint32_t*>(dstp + rr * a.pitch) = __byte_perm(__byte_perm(o[0], o[1], 0x0040), __byte_perm(o[2], o[3], 0x0040), 0x5410);
+    }
+}
+
+/* REFLECT_101 border of levels >= 1 (copyMakeBorder, src/ORBextractor.cc:1167-1168), all levels in one launch
+ * (gridDim.y = level - 1).  One thread = one 4-byte group that is not a full interior group.  A border pixel is a copy
+ * of the interior pixel it mirrors (all interior pixels are final when this kernel starts). */
+__global__ void __launch_bounds__(256) k_pyramid_borders(const __grid_constant__ ExDesc d, ExBuffers b) {
+    const int level = blockIdx.y + 1;
+    const LevelDesc& L = d.lv[level];
+    const int G = L.pitch >> 2, nInt = L.w >> 2, gFirst = ORBFE_ROW_LEAD / 4;
+    const int side = G - nInt;                                  /* border groups of an interior row */
+    const int nband = ORBFE_EDGE * G;                           /* groups of the top (or bottom) band */
+    int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    int row, g;
+    if (idx < nband) { row = idx / G; g = idx - row * G; }
+    else if (idx < 2 * nband) { idx -= nband; row = idx / G; g = idx - row * G; row += ORBFE_EDGE + L.h; }
+    else {
+        idx -= 2 * nband;
+        if (idx >= L.h * side) return;
+        row = idx / side;
+        const int j = idx - row * side;
+        g = j < gFirst ? j : nInt + j;
+        row += ORBFE_EDGE;
+    }
+    uint8_t* slab = b.pyr + (size_t)blockIdx.z * d.pyrSlab;
+    const uint8_t* lint = slab + (uint32_t)(L.pyrOff + ORBFE_EDGE * L.pitch + ORBFE_ROW_LEAD);   /* this level, interior (0,0) */
+    const int yi = reflect101(row - ORBFE_EDGE, L.h);
+    const int px0 = g * 4 - ORBFE_ROW_LEAD;
+    uint32_t out = 0;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const int px = px0 + k;
+        if (px < -ORBFE_EDGE || px >= L.w + ORBFE_EDGE) continue;
+        out |= (uint32_t)lint[yi * L.pitch + reflect101(px, L.w)] << (8 * k);   /* interior bytes of a partial group copy themselves */
+    }
+    *reinterpret_cast<uint32_t*>(slab + (uint32_t)(L.pyrOff + row * L.pitch + g * 4)) = out;
 }
 
 /* --------------------------------------------------------------------------------------------------- blur */
@@ -1257,12 +1269,15 @@ int orbfe_launch_extract(orbfe_extractor* ex, const uint8_t* d_images, int nfram
         const int items = (L.pitch >> 4) * (L.h + 2 * ORBFE_EDGE);
         k_pyramid_copy0<<<dim3((items + 255) / 256, nframes), 256, 0, st>>>(d, ex->b, d_images);
     }
+    int maxBorder = 0;
     for (int l = 1; l < d.nlevels; l++) {
         const LevelDesc& L = d.lv[l];
-        const int nInt = L.w >> 2, intWarps = (nInt + 31) / 32;
-        k_pyramid_level<<<dim3(intWarps + 1, (L.h + 2 * ORBFE_EDGE + 8 * PYR_ROWS - 1) / (8 * PYR_ROWS), nframes), dim3(32, 8), 0, st>>>(
+        const int nInt = L.w >> 2, G = L.pitch >> 2;
+        k_pyramid_level<<<dim3((nInt + 1 + 31) / 32, (L.h + 8 * PYR_ROWS - 1) / (8 * PYR_ROWS), nframes), dim3(32, 8), 0, st>>>(
             d, ex->b, ResizeArgs{L.w, L.h, L.pitch, L.pyrOff, d.lv[l - 1].pitch, d.lv[l - 1].pyrOff, L.tabX, L.tabY});
+        maxBorder = maxBorder > 2 * ORBFE_EDGE * G + L.h * (G - nInt) ? maxBorder : 2 * ORBFE_EDGE * G + L.h * (G - nInt);
     }
+    if (d.nlevels > 1) k_pyramid_borders<<<dim3((maxBorder + 255) / 256, d.nlevels - 1, nframes), 256, 0, st>>>(d, ex->b);
     STAGE_MARK();
     k_fast_stream<<<dim3((d.nStrips + FS_WARPS - 1) / FS_WARPS, nframes), FS_WARPS * 32, 0, st>>>(d, ex->b);
     k_fast_nms<<<dim3((d.nCells + FN_WARPS - 1) / FN_WARPS, nframes), FN_WARPS * 32, 0, st>>>(d, ex->b);
@@ -1281,7 +1296,7 @@ int orbfe_launch_extract(orbfe_extractor* ex, const uint8_t* d_images, int nfram
     STAGE_MARK();
 #undef STAGE_MARK
     if (prof) ex->stagePending = 1;
-    ex->launches += 2 * d.nlevels + 6;
+    ex->launches += 2 * d.nlevels + 6 + (d.nlevels > 1 ? 1 : 0);
     ORBFE_CUDA(cudaGetLastError());
     return 0;
 }
