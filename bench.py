@@ -375,7 +375,7 @@ def main():
                            "l2": "inputs_larger_than_L2 (%d MB of images per step per GPU)" % (2 * P * W * H >> 20),
                            "mean_keypoints_per_frame": nkp, "parallelism": "frames sharded by rank, no collective"},
                 "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
-                "gpu_launches": (2 * (2 * PARAMS[2] + 7) + 2) * args.steps,
+                "gpu_launches": (2 * (2 * PARAMS[2] + 7) + 3) * args.steps,
                 "hamming": hamming}
         print(json.dumps(line), flush=True)
     if world > 1:

@@ -750,7 +750,7 @@ __global__ void __launch_bounds__(FN_WARPS * 32) k_fast_nms(const __grid_constan
 }
 
 /* ----------------------------------------------------------------------------------------------- quadtree */
-#define QT_NT 512
+#define QT_NT 256
 
 /* In-place exclusive scan of data[0..n) by the whole CTA; returns the total. tmp: QT_NT/32+1 ints. */
 static __device__ int block_exscan(int* data, int n, int* tmp) {

@@ -268,6 +268,7 @@ int orbfe_extractor_create(const orbfe_params* p, int device, int width, int hei
     d.nCells = (int)cells.size();
     d.candCap = keyTotal;
     d.nStrips = (int)strips.size();
+    d.stBands = (height >> 3) + 1;
     d.rawCap = rawTotal;
     d.kpCap = selTotal;
     d.pyrSlab = align_up(pyrOff + 256, 256);
@@ -310,6 +311,8 @@ int orbfe_extractor_create(const orbfe_params* p, int device, int width, int hei
     TRY(dev_alloc(ex, &b.uRight, B * d.kpCap));
     TRY(dev_alloc(ex, &b.depth, B * d.kpCap));
     TRY(dev_alloc(ex, &b.sadBest, B * d.kpCap));
+    TRY(dev_alloc(ex, &b.stTable, B * d.kpCap));
+    TRY(dev_alloc(ex, &b.stBand, B * (d.stBands + 1)));
     TRY(dev_alloc(ex, &dCells, cells.size()));
     TRY(dev_alloc(ex, &dStrips, strips.size()));
     TRY(dev_alloc(ex, &b.raw, B * (size_t)d.rawCap));

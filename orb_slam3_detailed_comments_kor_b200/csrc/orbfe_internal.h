@@ -46,6 +46,7 @@ struct ExDesc {
     int kpCap;        /* selected keypoints per frame, all levels (= sum selCap) */
     int nodeCap;      /* quadtree node capacity (max over levels of selCap, padded) */
     int iniTh, minTh;
+    int stBands;      /* 8-row bands of the stereo candidate table: (H >> 3) + 1 */
     int nStrips;      /* strips of k_fast_stream per frame */
     int rawCap;       /* raw-corner slots per frame */
     int fastRows;     /* tallest FAST cell ROI (rows of the smem tile) */
@@ -100,6 +101,8 @@ struct ExBuffers {
     float* uRight;       /* [B][kpCap] */
     float* depth;        /* [B][kpCap] */
     int* sadBest;        /* [B][kpCap] stereo scratch: best SAD per left keypoint, -1 = no match */
+    uint4* stTable;      /* [B][kpCap] stereo scratch: this extractor's keypoints bucketed by 8-row band (x, band rows | octave, index) */
+    int* stBand;         /* [B][stBands+1] first table entry of each band */
     const CellDesc* cells;
     const uint2* tabs;   /* resize tables */
     const uint8_t* input; /* [B][H*W] staging for host-image entry points */

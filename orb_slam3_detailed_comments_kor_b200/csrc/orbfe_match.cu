@@ -171,32 +171,52 @@ static int launch_top2(const uint8_t* dQ, int nq, const uint8_t* dDb, long long 
 
 /* --------------------------------------------------------------------------------------------------- stereo */
 #define ST_NT 256
-#define ST_KPB 32   /* left keypoints per CTA */
-/* One CTA = 32 left keypoints of one frame, one warp = one left keypoint at a time.  The CTA first builds a compact
- * table of the frame's right keypoints in shared memory (x, row band [floor(y-r), ceil(y+r)], octave; r = 2*scale,
- * src/Frame.cc:814-824); lanes then stride over that table in index order (the reference's row lists are in index
- * order too), keep (distance, index) minima, and the warp does the 11-shift SAD and the parabola fit.  Float steps use
- * round-to-nearest intrinsics (no contraction). */
-__global__ void __launch_bounds__(ST_NT) k_stereo_match(const __grid_constant__ ExDesc d, ExBuffers L, ExBuffers R, float mbf,
-                                                        float minD, float maxD) {
-    extern __shared__ __align__(8) uint2 s_right[]; /* (x bits, minr | maxr<<12 | octave<<24) */
-    const size_t f = blockIdx.y;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int n = L.count[f], nR = R.count[f];
-    if ((int)blockIdx.x * ST_KPB >= n) return;
-    {
-        const orbfe_keypoint* kR = R.kps + f * d.kpCap;
-        for (int i = threadIdx.x; i < nR; i += ST_NT) {
-            const orbfe_keypoint k = kR[i];
-            const float r = __fmul_rn(2.0f, d.lv[k.octave].scale);
-            const int maxr = max(0, min(4095, (int)ceilf(__fadd_rn(k.y, r)))), minr = max(0, min(4095, (int)floorf(__fsub_rn(k.y, r))));
-            s_right[i] = make_uint2(__float_as_uint(k.x), (uint32_t)minr | ((uint32_t)maxr << 12) | ((uint32_t)k.octave << 24));
-        }
+#define ST_BANDSHIFT 3
+/* One CTA = one frame: bucket the right keypoints by the 8-row band of their y (counting sort in shared memory), so that
+ * the matcher only walks the bands that can hold candidates for a left keypoint's row instead of every right keypoint.
+ * Entry = (x bits, floor(y-r) | ceil(y+r) << 12 | octave << 24, original index, 0); r = 2*scale (src/Frame.cc:814-824). */
+__global__ void __launch_bounds__(256) k_stereo_bucket(const __grid_constant__ ExDesc d, ExBuffers R) {
+    extern __shared__ int s_cnt[];   /* [stBands + 1] */
+    const size_t f = blockIdx.x;
+    const int nR = R.count[f], nb = d.stBands;
+    for (int i = threadIdx.x; i <= nb; i += 256) s_cnt[i] = 0;
+    __syncthreads();
+    const orbfe_keypoint* kR = R.kps + f * d.kpCap;
+    for (int i = threadIdx.x; i < nR; i += 256) atomicAdd(&s_cnt[min(nb - 1, max(0, (int)kR[i].y) >> ST_BANDSHIFT)], 1);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int run = 0;
+        for (int i = 0; i < nb; i++) { const int c = s_cnt[i]; s_cnt[i] = run; run += c; }
+        s_cnt[nb] = run;
     }
     __syncthreads();
-    for (int it = warp; it < ST_KPB; it += ST_NT / 32) {
-        const int iL = blockIdx.x * ST_KPB + it;
-        if (iL >= n) break;
+    int* band = R.stBand + f * (nb + 1);
+    for (int i = threadIdx.x; i <= nb; i += 256) band[i] = s_cnt[i];
+    __syncthreads();
+    uint4* tab = R.stTable + f * d.kpCap;
+    for (int i = threadIdx.x; i < nR; i += 256) {
+        const orbfe_keypoint k = kR[i];
+        const float r = __fmul_rn(2.0f, d.lv[k.octave].scale);
+        const int maxr = max(0, min(4095, (int)ceilf(__fadd_rn(k.y, r)))), minr = max(0, min(4095, (int)floorf(__fsub_rn(k.y, r))));
+        const int slot = atomicAdd(&s_cnt[min(nb - 1, max(0, (int)k.y) >> ST_BANDSHIFT)], 1);
+        tab[slot] = make_uint4(__float_as_uint(k.x), (uint32_t)minr | ((uint32_t)maxr << 12) | ((uint32_t)k.octave << 24), (uint32_t)i, 0u);
+    }
+}
+
+#define ST_KPB 8   /* left keypoints per CTA = warps per CTA */
+/* One warp = one left keypoint.  Lanes stride over the right keypoints of the bands whose rows can reach this keypoint's
+ * row (a right keypoint covers rows [floor(y-r), ceil(y+r)] with r <= 2*maxScale), apply the reference's gates (row band,
+ * octave +-1, disparity range), keep (distance, original index) minima — the reference scans in index order with a
+ * strict `<`, i.e. the lowest index wins ties — then the warp does the 11-shift SAD and the parabola fit.  Float steps
+ * use round-to-nearest intrinsics (no contraction). */
+__global__ void __launch_bounds__(ST_NT) k_stereo_match(const __grid_constant__ ExDesc d, ExBuffers L, ExBuffers R, float mbf,
+                                                        float minD, float maxD) {
+    const size_t f = blockIdx.y;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int n = L.count[f];
+    {
+        const int iL = blockIdx.x * ST_KPB + warp;
+        if (iL >= n) return;
         const size_t o = f * d.kpCap + iL;
         float outU = -1.f, outD = -1.f;
         int outS = -1;
@@ -206,32 +226,42 @@ __global__ void __launch_bounds__(ST_NT) k_stereo_match(const __grid_constant__ 
         const int row = (int)vL;
         const float minU = __fsub_rn(uL, maxD), maxU = __fsub_rn(uL, minD);
         int best = 100, bestR = 0x7FFFFFFF; /* TH_HIGH, src/ORBmatcher.cc:36 */
+        float bestX = 0.f;
         if (!(maxU < 0)) {
             const uint4* dL = reinterpret_cast<const uint4*>(L.desc + o * 32);
             const uint4 dl0 = dL[0], dl1 = dL[1];
-            for (int iR = lane; iR < nR; iR += 32) {
-                const uint2 k = s_right[iR];
+            /* |(int)y - row| <= r + 2 with r <= 2 * scale of the coarsest level */
+            const int reach = (int)ceilf(__fmul_rn(2.0f, d.lv[d.nlevels - 1].scale)) + 2;
+            const int nb = d.stBands;
+            const int* band = R.stBand + f * (nb + 1);
+            const int b0 = max(0, (row - reach) >> ST_BANDSHIFT), b1 = min(nb - 1, (row + reach) >> ST_BANDSHIFT);
+            const int e0 = band[b0], e1 = band[b1 + 1];
+            const uint4* tab = R.stTable + f * d.kpCap;
+            for (int e = e0 + lane; e < e1; e += 32) {
+                const uint4 k = tab[e];
                 const int minr = k.y & 0xFFF, maxr = (k.y >> 12) & 0xFFF, oct = k.y >> 24;
                 if (row < minr || row > maxr) continue;
                 if (oct < levelL - 1 || oct > levelL + 1) continue;
                 const float uR = __uint_as_float(k.x);
                 if (uR >= minU && uR <= maxU) {
+                    const int iR = (int)k.z;
                     const uint4* dR = reinterpret_cast<const uint4*>(R.desc + (f * d.kpCap + iR) * 32);
-                    const uint4 b0 = dR[0], b1 = dR[1];
-                    const int dist = __popc(dl0.x ^ b0.x) + __popc(dl0.y ^ b0.y) + __popc(dl0.z ^ b0.z) + __popc(dl0.w ^ b0.w) +
-                                     __popc(dl1.x ^ b1.x) + __popc(dl1.y ^ b1.y) + __popc(dl1.z ^ b1.z) + __popc(dl1.w ^ b1.w);
-                    if (dist < best) { best = dist; bestR = iR; }
+                    const uint4 c0 = dR[0], c1 = dR[1];
+                    const int dist = __popc(dl0.x ^ c0.x) + __popc(dl0.y ^ c0.y) + __popc(dl0.z ^ c0.z) + __popc(dl0.w ^ c0.w) +
+                                     __popc(dl1.x ^ c1.x) + __popc(dl1.y ^ c1.y) + __popc(dl1.z ^ c1.z) + __popc(dl1.w ^ c1.w);
+                    if (dist < best || (dist == best && iR < bestR)) { best = dist; bestR = iR; bestX = uR; }
                 }
             }
 #pragma unroll
             for (int s = 16; s > 0; s >>= 1) {
                 const int ob = __shfl_xor_sync(0xFFFFFFFFu, best, s), oi = __shfl_xor_sync(0xFFFFFFFFu, bestR, s);
-                if (ob < best || (ob == best && oi < bestR)) { best = ob; bestR = oi; }
+                const float ox = __shfl_xor_sync(0xFFFFFFFFu, bestX, s);
+                if (ob < best || (ob == best && oi < bestR)) { best = ob; bestR = oi; bestX = ox; }
             }
         }
         if (best < 75 && !(maxU < 0)) { /* thOrbDist = (TH_HIGH+TH_LOW)/2, src/Frame.cc:802 */
             const LevelDesc& lv = d.lv[levelL];
-            const float uR0 = __uint_as_float(s_right[bestR].x);
+            const float uR0 = bestX;
             const float sf = __fdiv_rn(1.0f, lv.scale); /* mvInvScaleFactors[octave] */
             const float suL = roundf(__fmul_rn(kpL.x, sf)), svL = roundf(__fmul_rn(kpL.y, sf)), suR0 = roundf(__fmul_rn(uR0, sf));
             const float iniu = __fsub_rn(__fadd_rn(suR0, 5.f), 5.f), endu = __fadd_rn(__fadd_rn(__fadd_rn(suR0, 5.f), 5.f), 1.f);
@@ -355,15 +385,14 @@ int orbfe_stereo_match_batch_device(orbfe_extractor* exL, orbfe_extractor* exR, 
     ORBFE_CUDA(cudaSetDevice(exL->device));
     cudaStream_t st = stream ? (cudaStream_t)stream : exL->stream;
     if (!stream) ORBFE_CUDA(cudaStreamSynchronize(exR->stream)); /* right extraction ran on its own stream */
-    const size_t stSmem = (size_t)exL->d.kpCap * sizeof(uint2);
-    if (stSmem > 48 * 1024) ORBFE_CUDA(cudaFuncSetAttribute(k_stereo_match, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)stSmem));
     const bool prof = exL->profiling != 0;
     if (prof && exL->stereoPending) { int rc = orbfe_collect_stage_times(exL); if (rc) return rc; }
     cudaEvent_t* ev = exL->ev + ORBFE_NUM_STAGES + 1; /* two private events: the extractor's own stay untouched */
     if (prof) ORBFE_CUDA(cudaEventRecord(ev[0], st));
-    k_stereo_match<<<dim3((exL->d.kpCap + ST_KPB - 1) / ST_KPB, nframes), ST_NT, stSmem, st>>>(exL->d, exL->b, exR->b, mbf, minD, maxD);
+    k_stereo_bucket<<<nframes, 256, (exR->d.stBands + 1) * sizeof(int), st>>>(exR->d, exR->b);
+    k_stereo_match<<<dim3((exL->d.kpCap + ST_KPB - 1) / ST_KPB, nframes), ST_NT, 0, st>>>(exL->d, exL->b, exR->b, mbf, minD, maxD);
     k_stereo_median<<<nframes, 256, 0, st>>>(exL->d, exL->b);
-    exL->launches += 2;
+    exL->launches += 3;
     ORBFE_CUDA(cudaGetLastError());
     if (prof) {
         /* stereo is short: time both kernels as one span, reported under "stereo match" */
