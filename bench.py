@@ -314,7 +314,14 @@ def main():
     torch.cuda.synchronize()
     e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3 / args.steps)
     barrier()
+    # the host link's own speed for the same upload (pinned -> device), to read the e2e figure against
+    t0 = time.perf_counter()
+    for _ in range(3):
+        dL.copy_(hL, non_blocking=True); dR.copy_(hR, non_blocking=True)
+    torch.cuda.synchronize()
+    h2d_gbs = 3 * 2 * P * W * H / (time.perf_counter() - t0) / 1e9
     e2e = {"value": 2 * P * world / (e2e_ms / 1e3), "unit": "frames/s", "ms_per_step": e2e_ms,
+           "pinned_h2d_gbs_measured": h2d_gbs, "h2d_only_ms_per_step": 2 * P * W * H / h2d_gbs / 1e6,
            "h2d_bytes_per_step": 2 * P * W * H,
            "d2h_bytes_per_step": 2 * P * (cap * 60 + 8) + 2 * P * cap * 4}
 

@@ -1256,10 +1256,26 @@ int orbfe_configure_kernels(int quadSmem, int fastSmem) {
     return 0;
 }
 
-/* Enqueue the whole extractor for `nframes` device-resident frames on `st`. */
-int orbfe_launch_extract(orbfe_extractor* ex, const uint8_t* d_images, int nframes, int lap0, int lap1, cudaStream_t st) {
+/* The per-frame buffers as seen by a launch whose frame 0 is the object's frame f0 (chunked host pipeline). */
+static ExBuffers shift_frames(const ExBuffers& b, const ExDesc& d, int f0) {
+    ExBuffers s = b;
+    const size_t f = (size_t)f0;
+    s.pyr += f * d.pyrSlab; s.blur += f * d.blurSlab;
+    s.cand += f * d.candCap; s.cellCount += f * d.nCells; s.raw += f * (size_t)d.rawCap; s.rawCount += f * d.nCells;
+    s.keys += f * d.candCap; s.keyNode += f * d.candCap;
+    s.sel += f * d.kpCap; s.selCount += f * d.nlevels; s.work += f * d.kpCap;
+    s.kps += f * d.kpCap; s.desc += f * d.kpCap * 32; s.count += f; s.mono += f;
+    s.uRight += f * d.kpCap; s.depth += f * d.kpCap; s.sadBest += f * d.kpCap;
+    s.stTable += f * d.kpCap; s.stBand += f * (d.stBands + 1);
+    return s;
+}
+
+/* Enqueue the whole extractor for `nframes` device-resident frames on `st`; results land at the object's frames
+ * frame0 .. frame0+nframes-1 (frame0 != 0 only in the chunked host pipeline, which runs its chunks in stream order). */
+int orbfe_launch_extract(orbfe_extractor* ex, const uint8_t* d_images, int nframes, int lap0, int lap1, cudaStream_t st, int frame0) {
     const ExDesc& d = ex->d;
-    const bool prof = ex->profiling != 0;
+    const ExBuffers xb = frame0 ? shift_frames(ex->b, d, frame0) : ex->b;
+    const bool prof = ex->profiling != 0 && frame0 == 0;
     int e = 0;
 #define STAGE_MARK() do { if (prof) ORBFE_CUDA(cudaEventRecord(ex->ev[e++], st)); } while (0)
     if (prof && ex->stagePending) { int rc = orbfe_collect_stage_times(ex); if (rc) return rc; }
@@ -1267,32 +1283,32 @@ int orbfe_launch_extract(orbfe_extractor* ex, const uint8_t* d_images, int nfram
     {
         const LevelDesc& L = d.lv[0];
         const int items = (L.pitch >> 4) * (L.h + 2 * ORBFE_EDGE);
-        k_pyramid_copy0<<<dim3((items + 255) / 256, nframes), 256, 0, st>>>(d, ex->b, d_images);
+        k_pyramid_copy0<<<dim3((items + 255) / 256, nframes), 256, 0, st>>>(d, xb, d_images);
     }
     int maxBorder = 0;
     for (int l = 1; l < d.nlevels; l++) {
         const LevelDesc& L = d.lv[l];
         const int nInt = L.w >> 2, G = L.pitch >> 2;
         k_pyramid_level<<<dim3((nInt + 1 + 31) / 32, (L.h + 8 * PYR_ROWS - 1) / (8 * PYR_ROWS), nframes), dim3(32, 8), 0, st>>>(
-            d, ex->b, ResizeArgs{L.w, L.h, L.pitch, L.pyrOff, d.lv[l - 1].pitch, d.lv[l - 1].pyrOff, L.tabX, L.tabY});
+            d, xb, ResizeArgs{L.w, L.h, L.pitch, L.pyrOff, d.lv[l - 1].pitch, d.lv[l - 1].pyrOff, L.tabX, L.tabY});
         maxBorder = maxBorder > 2 * ORBFE_EDGE * G + L.h * (G - nInt) ? maxBorder : 2 * ORBFE_EDGE * G + L.h * (G - nInt);
     }
-    if (d.nlevels > 1) k_pyramid_borders<<<dim3((maxBorder + 255) / 256, d.nlevels - 1, nframes), 256, 0, st>>>(d, ex->b);
+    if (d.nlevels > 1) k_pyramid_borders<<<dim3((maxBorder + 255) / 256, d.nlevels - 1, nframes), 256, 0, st>>>(d, xb);
     STAGE_MARK();
-    k_fast_stream<<<dim3((d.nStrips + FS_WARPS - 1) / FS_WARPS, nframes), FS_WARPS * 32, 0, st>>>(d, ex->b);
-    k_fast_nms<<<dim3((d.nCells + FN_WARPS - 1) / FN_WARPS, nframes), FN_WARPS * 32, 0, st>>>(d, ex->b);
-    k_fast_cells_list<<<148 * 4, FAST_NT, ex->fastSmem, st>>>(d, ex->b);
+    k_fast_stream<<<dim3((d.nStrips + FS_WARPS - 1) / FS_WARPS, nframes), FS_WARPS * 32, 0, st>>>(d, xb);
+    k_fast_nms<<<dim3((d.nCells + FN_WARPS - 1) / FN_WARPS, nframes), FN_WARPS * 32, 0, st>>>(d, xb);
+    k_fast_cells_list<<<148 * 4, FAST_NT, ex->fastSmem, st>>>(d, xb);
     STAGE_MARK();
     for (int l = 0; l < d.nlevels; l++) {
         const LevelDesc& L = d.lv[l];
-        k_blur7<<<dim3((L.w + BLUR_TW - 1) / BLUR_TW, (L.h + BLUR_TH - 1) / BLUR_TH, nframes), 256, 0, st>>>(d, ex->b, l);
+        k_blur7<<<dim3((L.w + BLUR_TW - 1) / BLUR_TW, (L.h + BLUR_TH - 1) / BLUR_TH, nframes), 256, 0, st>>>(d, xb, l);
     }
     STAGE_MARK();
-    k_quadtree<<<dim3(d.nlevels, nframes), QT_NT, ex->quadSmem, st>>>(d, ex->b);
+    k_quadtree<<<dim3(d.nlevels, nframes), QT_NT, ex->quadSmem, st>>>(d, xb);
     STAGE_MARK();
-    k_assemble<<<nframes, AS_NT, 0, st>>>(d, ex->b, lap0, lap1);
+    k_assemble<<<nframes, AS_NT, 0, st>>>(d, xb, lap0, lap1);
     STAGE_MARK();
-    k_orient_describe<<<dim3((d.kpCap + OD_NT / 32 - 1) / (OD_NT / 32), nframes), OD_NT, 0, st>>>(d, ex->b);
+    k_orient_describe<<<dim3((d.kpCap + OD_NT / 32 - 1) / (OD_NT / 32), nframes), OD_NT, 0, st>>>(d, xb);
     STAGE_MARK();
 #undef STAGE_MARK
     if (prof) ex->stagePending = 1;

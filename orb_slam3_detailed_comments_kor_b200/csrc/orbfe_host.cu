@@ -14,7 +14,7 @@
 int orbfe_upload_constants(const int* umax16, const int8_t* pattern1024);
 int orbfe_quadtree_smem_bytes(int cap);
 int orbfe_configure_kernels(int quadSmem, int fastSmem);
-int orbfe_launch_extract(orbfe_extractor* ex, const uint8_t* d_images, int nframes, int lap0, int lap1, cudaStream_t st);
+int orbfe_launch_extract(orbfe_extractor* ex, const uint8_t* d_images, int nframes, int lap0, int lap1, cudaStream_t st, int frame0);
 int orbfe_collect_stage_times(orbfe_extractor* ex);
 
 static thread_local char g_err[512] = "";
@@ -83,6 +83,10 @@ void orbfe_extractor_destroy(orbfe_extractor* ex) {
     if (ex->hCount) cudaFreeHost(ex->hCount);
     if (ex->hMono) cudaFreeHost(ex->hMono);
     for (cudaEvent_t ev : ex->ev) if (ev) cudaEventDestroy(ev);
+    for (cudaEvent_t ev : ex->evIn) if (ev) cudaEventDestroy(ev);
+    for (cudaEvent_t ev : ex->evDone) if (ev) cudaEventDestroy(ev);
+    if (ex->copyIn) cudaStreamDestroy(ex->copyIn);
+    if (ex->copyOut) cudaStreamDestroy(ex->copyOut);
     if (ex->stream) cudaStreamDestroy(ex->stream);
     delete ex;
 }
@@ -112,7 +116,7 @@ int orbfe_extractor_create(const orbfe_params* p, int device, int width, int hei
     ex->maxBatch = max_batch;
     ex->lastBatch = 0;
     ex->params = *p;
-    ex->stream = nullptr;
+    ex->stream = nullptr; ex->copyIn = nullptr; ex->copyOut = nullptr;
     ex->hKps = nullptr; ex->hDesc = nullptr; ex->hCount = nullptr; ex->hMono = nullptr;
     ex->profiling = 0; ex->stagePending = 0; ex->stereoPending = 0; ex->launches = 0;
     memset(ex->ev, 0, sizeof ex->ev);
@@ -294,6 +298,12 @@ int orbfe_extractor_create(const orbfe_params* p, int device, int width, int hei
 #define TRY(x) do { rc = (x); if (rc) { orbfe_extractor_destroy(ex); return rc; } } while (0)
 #define TRYC(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { rc = orbfe_cuda_fail(e_, #x); orbfe_extractor_destroy(ex); return rc; } } while (0)
     TRYC(cudaStreamCreateWithFlags(&ex->stream, cudaStreamNonBlocking));
+    TRYC(cudaStreamCreateWithFlags(&ex->copyIn, cudaStreamNonBlocking));
+    TRYC(cudaStreamCreateWithFlags(&ex->copyOut, cudaStreamNonBlocking));
+    ex->evIn.assign((max_batch + ORBFE_HOST_CHUNK - 1) / ORBFE_HOST_CHUNK, nullptr);
+    ex->evDone.assign(ex->evIn.size(), nullptr);
+    for (cudaEvent_t& ev : ex->evIn) TRYC(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+    for (cudaEvent_t& ev : ex->evDone) TRYC(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
     for (cudaEvent_t& ev : ex->ev) TRYC(cudaEventCreate(&ev));
     TRY(dev_alloc(ex, &b.pyr, B * d.pyrSlab + 256));
     TRY(dev_alloc(ex, &b.blur, B * d.blurSlab + 256));
@@ -406,7 +416,7 @@ int orbfe_extract_batch_device(orbfe_extractor* ex, const uint8_t* d_images, int
     }
     ORBFE_CUDA(cudaSetDevice(ex->device));
     ex->lastBatch = nframes;
-    return orbfe_launch_extract(ex, d_images, nframes, lap0, lap1, stream ? (cudaStream_t)stream : ex->stream);
+    return orbfe_launch_extract(ex, d_images, nframes, lap0, lap1, stream ? (cudaStream_t)stream : ex->stream, 0);
 }
 
 int orbfe_batch_counts(orbfe_extractor* ex, int nframes, int32_t* n, int32_t* mono) {
@@ -448,30 +458,43 @@ int orbfe_extract_batch_host(orbfe_extractor* ex, const uint8_t* h_images, int n
     if (nframes < 1 || nframes > ex->maxBatch) { orbfe_set_error("nframes %d outside [1, max_batch=%d]", nframes, ex->maxBatch); return ORBFE_E_CAPACITY; }
     ORBFE_CUDA(cudaSetDevice(ex->device));
     const size_t frameBytes = (size_t)ex->d.W * ex->d.H;
-    cudaStream_t st = ex->stream;
-    ORBFE_CUDA(cudaMemcpyAsync(ex->inputStage, h_images, frameBytes * nframes, cudaMemcpyHostToDevice, st));
-    ex->lastBatch = nframes;
-    int rc = orbfe_launch_extract(ex, ex->inputStage, nframes, lap0, lap1, st);
-    if (rc) return rc;
     const int kc = ex->d.kpCap;
-    ORBFE_CUDA(cudaMemcpyAsync(ex->hCount, ex->b.count, nframes * sizeof(int), cudaMemcpyDeviceToHost, st));
-    ORBFE_CUDA(cudaMemcpyAsync(ex->hMono, ex->b.mono, nframes * sizeof(int), cudaMemcpyDeviceToHost, st));
-    if (cap >= kc) {
-        /* caller rows are at least as wide as ours: one strided copy each straight into the caller's arrays */
-        if (kps) ORBFE_CUDA(cudaMemcpy2DAsync(kps, (size_t)cap * sizeof(orbfe_keypoint), ex->b.kps, (size_t)kc * sizeof(orbfe_keypoint),
-                                             (size_t)kc * sizeof(orbfe_keypoint), nframes, cudaMemcpyDeviceToHost, st));
-        if (desc) ORBFE_CUDA(cudaMemcpy2DAsync(desc, (size_t)cap * 32, ex->b.desc, (size_t)kc * 32, (size_t)kc * 32, nframes, cudaMemcpyDeviceToHost, st));
-        ORBFE_CUDA(cudaStreamSynchronize(st));
-    } else {
-        if (kps) ORBFE_CUDA(cudaMemcpyAsync(ex->hKps, ex->b.kps, (size_t)nframes * kc * sizeof(orbfe_keypoint), cudaMemcpyDeviceToHost, st));
-        if (desc) ORBFE_CUDA(cudaMemcpyAsync(ex->hDesc, ex->b.desc, (size_t)nframes * kc * 32, cudaMemcpyDeviceToHost, st));
-        ORBFE_CUDA(cudaStreamSynchronize(st));
+    const bool direct = cap >= kc;   /* caller rows are at least as wide as ours: strided copies straight into the caller's arrays */
+    cudaStream_t st = ex->stream;
+    ex->lastBatch = nframes;
+    /* three-stage pipeline over chunks of frames: H2D of chunk k+1 (copyIn), kernels of chunk k (st), D2H of the results
+     * of chunk k-1 (copyOut) overlap; the chunks themselves run in order on `st` */
+    const int C = ORBFE_HOST_CHUNK;
+    for (int k = 0, f0 = 0; f0 < nframes; k++, f0 += C) {
+        const int nf = std::min(C, nframes - f0);
+        ORBFE_CUDA(cudaMemcpyAsync(ex->inputStage + (size_t)f0 * frameBytes, h_images + (size_t)f0 * frameBytes, frameBytes * nf, cudaMemcpyHostToDevice, ex->copyIn));
+        ORBFE_CUDA(cudaEventRecord(ex->evIn[k], ex->copyIn));
+        ORBFE_CUDA(cudaStreamWaitEvent(st, ex->evIn[k], 0));
+        int rc = orbfe_launch_extract(ex, ex->inputStage + (size_t)f0 * frameBytes, nf, lap0, lap1, st, f0);
+        if (rc) return rc;
+        ORBFE_CUDA(cudaEventRecord(ex->evDone[k], st));
+        ORBFE_CUDA(cudaStreamWaitEvent(ex->copyOut, ex->evDone[k], 0));
+        ORBFE_CUDA(cudaMemcpyAsync(ex->hCount + f0, ex->b.count + f0, nf * sizeof(int), cudaMemcpyDeviceToHost, ex->copyOut));
+        ORBFE_CUDA(cudaMemcpyAsync(ex->hMono + f0, ex->b.mono + f0, nf * sizeof(int), cudaMemcpyDeviceToHost, ex->copyOut));
+        const orbfe_keypoint* dk = ex->b.kps + (size_t)f0 * kc;
+        const uint8_t* dd = ex->b.desc + (size_t)f0 * kc * 32;
+        if (direct) {
+            if (kps) ORBFE_CUDA(cudaMemcpy2DAsync(kps + (size_t)f0 * cap, (size_t)cap * sizeof(orbfe_keypoint), dk, (size_t)kc * sizeof(orbfe_keypoint),
+                                                 (size_t)kc * sizeof(orbfe_keypoint), nf, cudaMemcpyDeviceToHost, ex->copyOut));
+            if (desc) ORBFE_CUDA(cudaMemcpy2DAsync(desc + (size_t)f0 * cap * 32, (size_t)cap * 32, dd, (size_t)kc * 32, (size_t)kc * 32, nf, cudaMemcpyDeviceToHost, ex->copyOut));
+        } else {
+            if (kps) ORBFE_CUDA(cudaMemcpyAsync(ex->hKps + (size_t)f0 * kc, dk, (size_t)nf * kc * sizeof(orbfe_keypoint), cudaMemcpyDeviceToHost, ex->copyOut));
+            if (desc) ORBFE_CUDA(cudaMemcpyAsync(ex->hDesc + (size_t)f0 * kc * 32, dd, (size_t)nf * kc * 32, cudaMemcpyDeviceToHost, ex->copyOut));
+        }
+    }
+    ORBFE_CUDA(cudaStreamSynchronize(ex->copyOut));
+    ORBFE_CUDA(cudaStreamSynchronize(st));
+    if (!direct)
         for (int f = 0; f < nframes; f++) {
             if (ex->hCount[f] > cap) { orbfe_set_error("caller capacity %d < %d keypoints (frame %d)", cap, ex->hCount[f], f); return ORBFE_E_CAPACITY; }
             if (kps) memcpy(kps + (size_t)f * cap, ex->hKps + (size_t)f * kc, (size_t)ex->hCount[f] * sizeof(orbfe_keypoint));
             if (desc) memcpy(desc + (size_t)f * cap * 32, ex->hDesc + (size_t)f * kc * 32, (size_t)ex->hCount[f] * 32);
         }
-    }
     for (int f = 0; f < nframes; f++) {
         if (n) n[f] = ex->hCount[f];
         if (mono) mono[f] = ex->hMono[f];
@@ -493,7 +516,7 @@ int orbfe_extract(orbfe_extractor* ex, const uint8_t* image, int rows, int cols,
     cudaStream_t st = ex->stream;
     ORBFE_CUDA(cudaMemcpy2DAsync(ex->inputStage, cols, image, step, cols, rows, cudaMemcpyHostToDevice, st));
     ex->lastBatch = 1;
-    int rc = orbfe_launch_extract(ex, ex->inputStage, 1, lap0, lap1, st);
+    int rc = orbfe_launch_extract(ex, ex->inputStage, 1, lap0, lap1, st, 0);
     if (rc) return rc;
     ORBFE_CUDA(cudaMemcpyAsync(ex->hCount, ex->b.count, sizeof(int), cudaMemcpyDeviceToHost, st));
     ORBFE_CUDA(cudaMemcpyAsync(ex->hMono, ex->b.mono, sizeof(int), cudaMemcpyDeviceToHost, st));

@@ -128,6 +128,33 @@ def test_batch_paths_agree_with_oracle():
     ex.close()
 
 
+def test_host_batch_pipeline_over_several_chunks():
+    """orbfe_extract_batch_host pipelines chunks of 32 frames (upload / kernels / download overlap): 70 frames = 3 chunks
+    must give exactly what the one-launch device path gives, and what the oracle gives on sampled frames."""
+    import torch
+    W, H, params, nb = 320, 240, (500, 1.2, 8, 20, 7), 70
+    imgs = np.stack([synth.frame(300 + i, W, H) for i in range(nb)])
+    ex = ORBextractor(*params, width=W, height=H, max_batch=nb)
+    cnt, mono, kps, desc = ex.extract_batch_host(imgs, (0, 160))
+    kps, desc = kps.copy(), desc.copy()
+    d_imgs = torch.from_numpy(imgs).cuda()
+    torch.cuda.synchronize()
+    ex.extract_batch_device(d_imgs.data_ptr(), nb, (0, 160), torch.cuda.Stream().cuda_stream)
+    torch.cuda.synchronize()
+    cnt2, mono2 = ex.batch_counts(nb)
+    assert np.array_equal(cnt, cnt2) and np.array_equal(mono, mono2) and cnt.min() > 50
+    orc = O.OracleExtractor(*params)
+    for f in range(nb):
+        m2, k2, d2 = ex.batch_result(f)
+        assert np.array_equal(kps[f, :cnt[f]], k2) and np.array_equal(desc[f, :cnt[f]], d2), "frame %d" % f
+        if f in (0, 31, 32, 63, 64, 69):
+            omono, okps, odesc = orc(imgs[f], (0, 160))
+            assert omono == mono[f]
+            assert_same_keypoints(k2, okps, "frame %d" % f)
+            assert np.array_equal(d2, odesc)
+    ex.close()
+
+
 def test_error_behaviour():
     ex = ORBextractor(1200, 1.2, 8, 20, 7, width=752, height=480)
     mono, kps, desc = ex(np.zeros((0, 0), np.uint8))
