@@ -94,22 +94,12 @@ __global__ void __launch_bounds__(256) k_pyramid_level(const __grid_constant__ E
     const int row0 = (blockIdx.y * 8 + threadIdx.y) * PYR_ROWS;   /* interior row */
     if (row0 >= a.h) return;
     const int tx = blockIdx.x * 32 + threadIdx.x;
-    if (tx > (a.w >> 2)) return;
+    if (tx >= ((a.w + 3) >> 2)) return;   /* a partial last group (w % 4 != 0) is computed like a full one, see the x table */
     uint8_t* slab = b.pyr + (size_t)blockIdx.z * d.pyrSlab;
     const uint8_t* sint = slab + (uint32_t)(a.spyrOff + ORBFE_EDGE * a.spitch + ORBFE_ROW_LEAD);
     const int px0 = tx * 4;
     uint8_t* dstp = slab + (uint32_t)(a.pyrOff + (row0 + ORBFE_EDGE) * a.pitch + ORBFE_ROW_LEAD + px0);
     const uint2* tabY = b.tabs + a.tabY;
-    if (tx == (a.w >> 2)) {
-        /* the last 1-3 columns when w % 4 != 0: one lane per row block, byte by byte */
-        for (int rr = 0; rr < PYR_ROWS && row0 + rr < a.h; rr++) {
-            const uint2 yt = __ldg(tabY + row0 + rr);
-            const uint8_t* r0 = sint + (uint32_t)((int)yt.x * a.spitch);
-            for (int px = px0; px < a.w; px++)
-                dstp[rr * a.pitch + px - px0] = (uint8_t)resize_px_generic(r0, r0 + a.spitch, __ldg(b.tabs + a.tabX + px), yt.y & 0xFFFF, yt.y >> 16);
-        }
-        return;
-    }
     const uint4* tp = reinterpret_cast<const uint4*>(b.tabs + a.tabX + px0); /* tabX is 4-entry aligned */
     const uint4 ta = __ldg(tp), tb = __ldg(tp + 1); /* entries (sx, c0|c1<<16) of the four pixels */
     uint2 yt[PYR_ROWS];
@@ -170,11 +160,16 @@ __global__ void __launch_bounds__(256) k_pyramid_borders(const __grid_constant__
     const int yi = reflect101(row - ORBFE_EDGE, L.h);
     const int px0 = g * 4 - ORBFE_ROW_LEAD;
     uint32_t out = 0;
+    const uint8_t* srow = lint + yi * L.pitch;
+    if (px0 >= 0 && px0 + 4 <= L.w) {
+        out = *reinterpret_cast<const uint32_t*>(srow + px0);                   /* top / bottom band above interior columns */
+    } else {
 #pragma unroll
-    for (int k = 0; k < 4; k++) {
-        const int px = px0 + k;
-        if (px < -ORBFE_EDGE || px >= L.w + ORBFE_EDGE) continue;
-        out |= (uint32_t)lint[yi * L.pitch + reflect101(px, L.w)] << (8 * k);   /* interior bytes of a partial group copy themselves */
+        for (int k = 0; k < 4; k++) {
+            const int px = px0 + k;
+            if (px < -ORBFE_EDGE || px >= L.w + ORBFE_EDGE) continue;
+            out |= (uint32_t)srow[reflect101(px, L.w)] << (8 * k);              /* interior bytes of a partial group copy themselves */
+        }
     }
     *reinterpret_cast<uint32_t*>(slab + (uint32_t)(L.pyrOff + row * L.pitch + g * 4)) = out;
 }
@@ -1289,7 +1284,7 @@ int orbfe_launch_extract(orbfe_extractor* ex, const uint8_t* d_images, int nfram
     for (int l = 1; l < d.nlevels; l++) {
         const LevelDesc& L = d.lv[l];
         const int nInt = L.w >> 2, G = L.pitch >> 2;
-        k_pyramid_level<<<dim3((nInt + 1 + 31) / 32, (L.h + 8 * PYR_ROWS - 1) / (8 * PYR_ROWS), nframes), dim3(32, 8), 0, st>>>(
+        k_pyramid_level<<<dim3(((L.w + 3) / 4 + 31) / 32, (L.h + 8 * PYR_ROWS - 1) / (8 * PYR_ROWS), nframes), dim3(32, 8), 0, st>>>(
             d, xb, ResizeArgs{L.w, L.h, L.pitch, L.pyrOff, d.lv[l - 1].pitch, d.lv[l - 1].pyrOff, L.tabX, L.tabY});
         maxBorder = maxBorder > 2 * ORBFE_EDGE * G + L.h * (G - nInt) ? maxBorder : 2 * ORBFE_EDGE * G + L.h * (G - nInt);
     }

@@ -251,6 +251,9 @@ int orbfe_extractor_create(const orbfe_params* p, int device, int width, int hei
             while (tabs.size() % 4) tabs.push_back(make_uint2(0, 0)); /* k_pyramid_level reads tabX four entries at a time */
             L.tabX = (int)tabs.size();
             linear_table(d.lv[l - 1].w, L.w, tabs);
+            /* the last column group may be partial (w % 4 != 0): it runs through the same four-pixel path with the last
+               entry repeated; the 1-3 surplus bytes fall in the border, which k_pyramid_borders rewrites afterwards */
+            while ((tabs.size() - L.tabX) % 4) tabs.push_back(tabs.back());
             for (int x = 0; x + 3 < L.w; x += 4)
                 if (tabs[L.tabX + x + 3].x - tabs[L.tabX + x].x > 6) {
                     orbfe_set_error("scale factor too large for the resize kernel's 8-byte source window");
