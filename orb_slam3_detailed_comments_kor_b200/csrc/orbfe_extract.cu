@@ -590,26 +590,23 @@ __global__ void __launch_bounds__(FS_WARPS * 32, 8) k_fast_stream(const __grid_c
             s_hits[warp][r][lane] = fast_sieve4(cen, top, bot, __byte_perm(lw, cen, 0x4321), __byte_perm(cen, rw, 0x6543), k127mt) & vmask;
         }
         __syncwarp();
-        /* 2. compaction: lane counts the survivors of its columns over the chunk, one scan gives its queue offset */
-        int cnt = 0;
-        for (int r = 0; r < rows; r++) cnt += __popc(s_hits[warp][r][lane]);
-        int incl = cnt;
+        /* 2. compaction in (row, byte, lane) order: one ballot per byte position of each row gives every survivor its
+         *    queue slot; consecutive entries then sit in different columns, i.e. different shared-memory banks */
+        int n = 0;
+        const uint32_t ltmask = (1u << lane) - 1;
+        for (int r = 0; r < rows; r++) {
+            const uint32_t h = s_hits[warp][r][lane];
+            if (!__any_sync(0xFFFFFFFFu, h != 0)) continue;
+            const int ent = r * (4 * FS_PW) + 4 * lane;                          /* byte offset of my byte 0 from bufb */
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const int t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
-            if (lane >= o) incl += t;
-        }
-        const int n = __shfl_sync(0xFFFFFFFFu, incl, 31);
-        if (n > 0) {
-            int off = incl - cnt;
-            for (int r = 0; r < rows; r++) {
-                uint32_t h = s_hits[warp][r][lane];
-                while (h) {
-                    const int bit = __ffs(h) - 1;
-                    h &= h - 1;
-                    q[off++] = (uint16_t)(r * (4 * FS_PW) + 4 * lane + (bit >> 3));     /* byte offset of the pixel from bufb */
-                }
+            for (int k = 0; k < 4; k++) {
+                const bool on = (h >> (8 * k + 7)) & 1u;
+                const uint32_t bal = __ballot_sync(0xFFFFFFFFu, on);
+                if (on) q[n + __popc(bal & ltmask)] = (uint16_t)(ent + k);
+                n += __popc(bal);
             }
+        }
+        if (n > 0) {
             __syncwarp();
             /* 3. exact test over the queue; corners are written back at the front of the queue */
             int m = 0;
