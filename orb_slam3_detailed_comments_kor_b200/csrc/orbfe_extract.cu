@@ -17,6 +17,7 @@
 #include <stdint.h>
 
 #include "orbfe_internal.h"
+#include "orbfe_trig.cuh"
 
 __constant__ int c_umax[16];
 __device__ __align__(16) float g_patternf[1024];   /* bit_pattern_31_ as floats: (x0,y0,x1,y1) per test */
@@ -66,12 +67,6 @@ __global__ void __launch_bounds__(256) k_pyramid_copy0(const __grid_constant__ E
  * them to the first tap, and form every horizontal tap pair with one PRMT + one DP2A
  * (c0*S[sx] + c1*S[sx+1], 16-bit coefficients x 8-bit pixels); groups that touch the border recompute the reflected
  * interior pixel byte-wise.  Arithmetic is OpenCV's 11-bit fixed point. */
-static __device__ __forceinline__ uint32_t resize_px_generic(const uint8_t* r0, const uint8_t* r1, uint2 xt, int b0, int b1) {
-    const int c0 = xt.y & 0xFFFF, c1 = xt.y >> 16;
-    const int h0 = r0[xt.x] * c0 + r0[xt.x + 1] * c1;
-    const int h1 = r1[xt.x] * c0 + r1[xt.x + 1] * c1;
-    return (uint32_t)((((b0 * (h0 >> 4)) >> 16) + ((b1 * (h1 >> 4)) >> 16) + 2) >> 2);
-}
 
 #define PYR_ROWS 4   /* output rows per thread: the horizontal tables, selectors and shifts are shared between them */
 /* Geometry of one resize launch, passed by value so that every field sits at a fixed constant-bank address. */
@@ -1183,13 +1178,9 @@ __global__ void __launch_bounds__(OD_NT) k_orient_describe(const __grid_constant
     }
     const float angle = fast_atan2_deg((float)m01, (float)m10);
 
-    /* computeOrbDescriptor, src/ORBextractor.cc:106-145.  cosf/sinf of the host libm are reproduced by the
-     * correctly-rounded value (double evaluation rounded once); see DESIGN.md "float reproducibility". */
-    const float factorPI = (float)(3.14159265358979323846 / 180.0);
-    const float ang = __fmul_rn(angle, factorPI);
-    double sd, cd;
-    sincos((double)ang, &sd, &cd);
-    const float ca = (float)cd, sa = (float)sd;
+    /* computeOrbDescriptor, src/ORBextractor.cc:106-145; a = cosf, b = sinf exactly as the host libm (orbfe_trig.cuh) */
+    float ca, sa;
+    orbfe_rotation(angle, &ca, &sa);
     const int bpitch = L.bpitch;
     const uint8_t* cb = b.blur + f * d.blurSlab + (uint32_t)(L.blurOff + y * bpitch + x);
     const float4* pt = reinterpret_cast<const float4*>(s_pat) + lane;   /* [test pair k][lane]: conflict-free */
@@ -1232,6 +1223,7 @@ int orbfe_upload_constants(const int* umax16, const int8_t* pattern1024) {
     ORBFE_CUDA(cudaMemcpyToSymbol(c_umax, umax16, 16 * sizeof(int)));
     ORBFE_CUDA(cudaMemcpyToSymbol(g_patternf, pf, sizeof pf));
     ORBFE_CUDA(cudaMemcpyToSymbol(c_rowmask, rowmask, sizeof rowmask));
+    ORBFE_CUDA(orbfe_trig_init());
     return 0;
 }
 
