@@ -325,6 +325,17 @@ def main():
            "h2d_bytes_per_step": 2 * P * W * H,
            "d2h_bytes_per_step": 2 * P * (cap * 60 + 8) + 2 * P * cap * 4}
 
+    # ---- single-frame latency through the reference-facing call (config 1: one 752x480 frame, host image in, results out)
+    ex1 = ORBextractor(*PARAMS, width=W, height=H, device=local_rank, max_batch=1)
+    one = hL.numpy()[0]
+    for _ in range(5):
+        ex1(one)
+    t0 = time.perf_counter()
+    for _ in range(20):
+        ex1(one)
+    single_ms = (time.perf_counter() - t0) * 1e3 / 20
+    ex1.close()
+
     # ---- Hamming top-2 (config 5): database sharded over the ranks, NCCL all-gather of the per-shard top-2 + merge
     from orb_slam3_detailed_comments_kor_b200 import sharding
     nq, ndb = args.hamming_queries, args.hamming_db
@@ -382,6 +393,7 @@ def main():
                            "l2": "inputs_larger_than_L2 (%d MB of images per step per GPU)" % (2 * P * W * H >> 20),
                            "mean_keypoints_per_frame": nkp, "parallelism": "frames sharded by rank, no collective"},
                 "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
+                "single_frame_latency_ms": single_ms,
                 "gpu_launches": (2 * (2 * PARAMS[2] + 7) + 3) * args.steps,
                 "hamming": hamming}
         print(json.dumps(line), flush=True)

@@ -1281,7 +1281,7 @@ int orbfe_launch_extract(orbfe_extractor* ex, const uint8_t* d_images, int nfram
     STAGE_MARK();
     k_fast_stream<<<dim3((d.nStrips + FS_WARPS - 1) / FS_WARPS, nframes), FS_WARPS * 32, 0, st>>>(d, xb);
     k_fast_nms<<<dim3((d.nCells + FN_WARPS - 1) / FN_WARPS, nframes), FN_WARPS * 32, 0, st>>>(d, xb);
-    k_fast_cells_list<<<148 * 4, FAST_NT, ex->fastSmem, st>>>(d, xb);
+    k_fast_cells_list<<<148 * 8, FAST_NT, ex->fastSmem, st>>>(d, xb);
     STAGE_MARK();
     for (int l = 0; l < d.nlevels; l++) {
         const LevelDesc& L = d.lv[l];
