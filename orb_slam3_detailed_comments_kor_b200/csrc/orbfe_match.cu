@@ -24,9 +24,16 @@ int orbfe_collect_stage_times(orbfe_extractor* ex);
 #define T2_QTILE (T2_NT * T2_QPT)   /* queries per CTA */
 #define T2_CHUNK 256                /* database rows per shared-memory stage (8 KB) */
 
+/* 256-bit Hamming distance = DescriptorDistance (src/ORBmatcher.cc:2591-2607).  POPC issues on the XU pipe at a
+ * quarter of the logic rate; LOP3/IADD go to the ALU pipe.  ncu on the 4096 x 2^20 search: eight plain population
+ * counts -> XU pipe 97 % busy, ALU half idle (5.58e11 pairs/s); a full carry-save tree (4 POPC + 14 LOP3) -> ALU pipe
+ * 94 % busy, XU 49 % (5.61e11); two full adders in front of six population counts balance the two pipes (6.78e11). */
 static __device__ __forceinline__ int ham256(const uint32_t (&q)[8], const uint4 a, const uint4 b) {
-    return __popc(q[0] ^ a.x) + __popc(q[1] ^ a.y) + __popc(q[2] ^ a.z) + __popc(q[3] ^ a.w) +
-           __popc(q[4] ^ b.x) + __popc(q[5] ^ b.y) + __popc(q[6] ^ b.z) + __popc(q[7] ^ b.w);
+    const uint32_t x0 = q[0] ^ a.x, x1 = q[1] ^ a.y, x2 = q[2] ^ a.z, x3 = q[3] ^ a.w;
+    const uint32_t x4 = q[4] ^ b.x, x5 = q[5] ^ b.y, x6 = q[6] ^ b.z, x7 = q[7] ^ b.w;
+    const uint32_t s0 = x0 ^ x1 ^ x2, c0 = (x0 & x1) | (x2 & (x0 ^ x1));   /* x0 + x1 + x2 = s0 + 2*c0, bitwise */
+    const uint32_t s1 = x3 ^ x4 ^ x5, c1 = (x3 & x4) | (x5 & (x3 ^ x4));
+    return __popc(s0) + __popc(s1) + __popc(x6) + __popc(x7) + 2 * (__popc(c0) + __popc(c1));
 }
 
 static __device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
