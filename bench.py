@@ -279,8 +279,19 @@ def main():
     peak = float(peaks.get("hbm_gbs", 6650.0))
     top_bytes = per_stage_bytes[STAGES[top]] * 2 * P
     achieved = top_bytes / (stage_ms_per_step[top] / 1e3) / 1e9 if stage_ms_per_step[top] > 0 else 0.0
-    roofline = {"bound": "hbm", "kernel": STAGES[top], "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak, "traffic": None,
+    traffic = None
+    try:   # DRAM bytes of the stage from the committed `ncu --set full` capture (profiles/r1_traffic.json), per launch
+        tj = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json")))
+        traffic = tj["dram_bytes_per_frame"].get(STAGES[top])
+        traffic = None if traffic is None else traffic * 2 * P
+    except (OSError, KeyError, ValueError):
+        pass
+    stage_kernels = {"pyramid": "k_pyramid_copy0 + 7 x k_pyramid_level + k_pyramid_borders",
+                     "fast": "k_fast_stream + k_fast_nms + k_fast_cells_list", "blur": "8 x k_blur7", "quadtree": "k_quadtree",
+                     "assemble": "k_assemble", "orient_describe": "k_orient_describe"}
+    roofline = {"bound": "hbm", "kernel": STAGES[top], "kernels": stage_kernels.get(STAGES[top]), "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": achieved / peak, "traffic": traffic,
+                "limiter": "integer issue (ncu: ALU pipe ~70 % busy, DRAM ~6 % of peak; profiles/r1_kernels_full.txt), not HBM",
                 "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured copy)" if peaks else "fallback 6650 GB/s",
                 "algorithmic_bytes_per_launch": top_bytes,
                 "launch_ms": float(stage_ms_per_step[top]),

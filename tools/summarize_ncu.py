@@ -62,5 +62,48 @@ def full(src, dst):
     print(open(dst).read())
 
 
-if __name__ == "__main__":
+
+
+def table(src, dst, frames):
+    """All kernels of one captured step: duration, DRAM traffic, issue/pipe utilisation, occupancy, top stalls;
+    plus profiles/<round>_traffic.json = DRAM bytes per frame per stage (what bench.py reports as roofline.traffic)."""
+    import json
+    out = subprocess.run(["ncu", "-i", src, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(out.splitlines()))
+    hdr = rows[0]
+    c = hdr.index
+    cols = [("us", "gpu__time_duration.sum"), ("dram_rd_MB", "dram__bytes_read.sum"), ("dram_wr_MB", "dram__bytes_write.sum"),
+            ("issue%", "smsp__issue_active.avg.pct_of_peak_sustained_active"), ("alu%", "sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active"),
+            ("xu%", "sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active"), ("lsu%", "sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active"),
+            ("dram%", "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed"), ("warps%", "sm__warps_active.avg.pct_of_peak_sustained_active"),
+            ("regs", "launch__registers_per_thread"), ("winst", "smsp__inst_executed.sum")]
+    stage_of = {"k_pyramid_copy0": "pyramid", "k_pyramid_level": "pyramid", "k_pyramid_borders": "pyramid", "k_fast_stream": "fast",
+                "k_fast_nms": "fast", "k_fast_cells_list": "fast", "k_blur7": "blur", "k_quadtree": "quadtree", "k_assemble": "assemble",
+                "k_orient_describe": "orient_describe", "k_stereo_bucket": "stereo", "k_stereo_match": "stereo", "k_stereo_median": "stereo"}
+    seen, traffic, times = {}, collections.OrderedDict(), collections.OrderedDict()
+    with open(dst, "w") as f:
+        f.write("# ncu --set full --clock-control none, one whole step of bench.py (%d frames per launch); source: %s\n" % (frames, src))
+        f.write("%-20s %-15s " % ("kernel", "grid") + " ".join("%10s" % n for n, _ in cols) + "  top stalls (per issue)\n")
+        for r in rows[2:]:
+            name = r[c("Kernel Name")].split("(")[0]
+            key = (name, r[c("Grid Size")])
+            if key in seen:
+                continue
+            seen[key] = 1
+            st = sorted(((float(r[i]), h) for i, h in enumerate(hdr) if h.startswith("smsp__average_warps_issue_stalled") and r[i] not in ("", "n/a")), reverse=True)[:3]
+            stalls = ", ".join("%s %.1f" % (h.replace("smsp__average_warps_issue_stalled_", "").replace("_per_issue_active.ratio", ""), v) for v, h in st)
+            f.write("%-20s %-15s " % (name, r[c("Grid Size")].replace(" ", "")) + " ".join("%10.10s" % r[c(m)] for _, m in cols) + "  " + stalls + "\n")
+            stg = stage_of.get(name)
+            if stg:
+                mb = float(r[c("dram__bytes_read.sum")]) + float(r[c("dram__bytes_write.sum")])
+                traffic[stg] = traffic.get(stg, 0.0) + mb * 1e6 / frames
+                times[stg] = times.get(stg, 0.0) + float(r[c("gpu__time_duration.sum")])
+    json.dump({"frames_per_launch": frames, "dram_bytes_per_frame": traffic, "stage_us_under_ncu": times, "source": src},
+              open(dst.replace("_kernels_full.txt", "_traffic.json"), "w"), indent=1)
+    print(open(dst).read())
+
+
+if __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "table":
+    table(sys.argv[2], sys.argv[3], int(sys.argv[4]))
+if __name__ == "__main__" and sys.argv[1] in ("launches", "full"):
     {"launches": launches, "full": full}[sys.argv[1]](sys.argv[2], sys.argv[3])
