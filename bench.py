@@ -310,9 +310,14 @@ def main():
     hd = torch.empty((P, cap), dtype=torch.float32, pin_memory=True).numpy()
     hLn, hRn = hL.numpy(), hR.numpy()
 
+    pool2 = ThreadPoolExecutor(2)
+
     def e2e_step():
-        exL.extract_batch_host(hLn, (0, 0), outL)
-        exR.extract_batch_host(hRn, (0, 0), outR)
+        # left and right extraction from two host threads on two extractor objects, as Frame's constructor does
+        # (src/Frame.cc:119-122); each call pipelines upload / kernels / download on its own streams
+        fl = pool2.submit(exL.extract_batch_host, hLn, (0, 0), outL)
+        fr = pool2.submit(exR.extract_batch_host, hRn, (0, 0), outR)
+        fl.result(); fr.result()
         M.compute_stereo_matches(exL, exR, P, MBF, 0.0, FX)
         _lib.check(L.orbfe_stereo_result_batch(exL.handle, P, _lib.ptr(hu), _lib.ptr(hd), cap))
 

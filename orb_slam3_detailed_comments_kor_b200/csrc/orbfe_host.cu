@@ -4,6 +4,7 @@
 #include <math.h>
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -303,7 +304,9 @@ int orbfe_extractor_create(const orbfe_params* p, int device, int width, int hei
     TRYC(cudaStreamCreateWithFlags(&ex->stream, cudaStreamNonBlocking));
     TRYC(cudaStreamCreateWithFlags(&ex->copyIn, cudaStreamNonBlocking));
     TRYC(cudaStreamCreateWithFlags(&ex->copyOut, cudaStreamNonBlocking));
-    ex->evIn.assign((max_batch + ORBFE_HOST_CHUNK - 1) / ORBFE_HOST_CHUNK, nullptr);
+    ex->hostChunk = ORBFE_HOST_CHUNK;
+    if (const char* e = getenv("ORBFE_HOST_CHUNK")) { const int v = atoi(e); if (v >= 1) ex->hostChunk = v; }
+    ex->evIn.assign((max_batch + ex->hostChunk - 1) / ex->hostChunk, nullptr);
     ex->evDone.assign(ex->evIn.size(), nullptr);
     for (cudaEvent_t& ev : ex->evIn) TRYC(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
     for (cudaEvent_t& ev : ex->evDone) TRYC(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
@@ -467,7 +470,7 @@ int orbfe_extract_batch_host(orbfe_extractor* ex, const uint8_t* h_images, int n
     ex->lastBatch = nframes;
     /* three-stage pipeline over chunks of frames: H2D of chunk k+1 (copyIn), kernels of chunk k (st), D2H of the results
      * of chunk k-1 (copyOut) overlap; the chunks themselves run in order on `st` */
-    const int C = ORBFE_HOST_CHUNK;
+    const int C = ex->hostChunk;
     for (int k = 0, f0 = 0; f0 < nframes; k++, f0 += C) {
         const int nf = std::min(C, nframes - f0);
         ORBFE_CUDA(cudaMemcpyAsync(ex->inputStage + (size_t)f0 * frameBytes, h_images + (size_t)f0 * frameBytes, frameBytes * nf, cudaMemcpyHostToDevice, ex->copyIn));

@@ -12,7 +12,7 @@
 #define ORBFE_EDGE 19        /* EDGE_THRESHOLD, src/ORBextractor.cc:72 */
 #define ORBFE_MIN_BORDER 16  /* EDGE_THRESHOLD-3, src/ORBextractor.cc:771 */
 #define ORBFE_NUM_STAGES 6   /* pyramid, fast, blur, quadtree, assemble, orient+describe (+2 stereo) */
-#define ORBFE_HOST_CHUNK 32   /* frames per stage of orbfe_extract_batch_host's copy/compute pipeline */
+#define ORBFE_HOST_CHUNK 64   /* frames per stage of orbfe_extract_batch_host's copy/compute pipeline */
 #define ORBFE_ROW_LEAD 32    /* byte of a padded row where interior x = 0 sits (16-byte aligned) */
 
 /* Geometry of one pyramid level; identical for every frame of a batch. */
@@ -119,7 +119,8 @@ struct orbfe_extractor {
     uint8_t* inputStage;  /* device copy of host images */
     cudaStream_t stream;
     cudaStream_t copyIn, copyOut;          /* host-batch pipeline: uploads and downloads overlap the kernels */
-    std::vector<cudaEvent_t> evIn, evDone; /* one pair per chunk of ORBFE_HOST_CHUNK frames */
+    std::vector<cudaEvent_t> evIn, evDone; /* one pair per chunk of hostChunk frames */
+    int hostChunk;                         /* frames per pipeline stage (ORBFE_HOST_CHUNK, or env ORBFE_HOST_CHUNK) */
     std::vector<float> scale, invScale, sigma2, invSigma2;
     std::vector<int> quota, umax;
     std::vector<void*> allocs;

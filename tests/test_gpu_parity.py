@@ -129,10 +129,10 @@ def test_batch_paths_agree_with_oracle():
 
 
 def test_host_batch_pipeline_over_several_chunks():
-    """orbfe_extract_batch_host pipelines chunks of 32 frames (upload / kernels / download overlap): 70 frames = 3 chunks
+    """orbfe_extract_batch_host pipelines chunks of 64 frames (upload / kernels / download overlap): 150 frames = 3 chunks
     must give exactly what the one-launch device path gives, and what the oracle gives on sampled frames."""
     import torch
-    W, H, params, nb = 320, 240, (500, 1.2, 8, 20, 7), 70
+    W, H, params, nb = 320, 240, (500, 1.2, 8, 20, 7), 150
     imgs = np.stack([synth.frame(300 + i, W, H) for i in range(nb)])
     ex = ORBextractor(*params, width=W, height=H, max_batch=nb)
     cnt, mono, kps, desc = ex.extract_batch_host(imgs, (0, 160))
@@ -147,7 +147,7 @@ def test_host_batch_pipeline_over_several_chunks():
     for f in range(nb):
         m2, k2, d2 = ex.batch_result(f)
         assert np.array_equal(kps[f, :cnt[f]], k2) and np.array_equal(desc[f, :cnt[f]], d2), "frame %d" % f
-        if f in (0, 31, 32, 63, 64, 69):
+        if f in (0, 63, 64, 127, 128, 149):
             omono, okps, odesc = orc(imgs[f], (0, 160))
             assert omono == mono[f]
             assert_same_keypoints(k2, okps, "frame %d" % f)
