@@ -25,6 +25,14 @@ SHAPES = {
     "kitti": (1241, 376, 2, (2000, 1.2, 8, 20, 7), [(0, 0), (0, 1000)]),
     "small": (160, 120, 3, (300, 1.2, 4, 20, 7), [(0, 0)]),
     "init5x": (752, 480, 11, (6000, 1.2, 8, 20, 7), [(0, 1000)]),     # mpIniORBextractor, src/Tracking.cc:1157
+    # shapes and parameters off the beaten path: widths that are not multiples of 4 / 16, other scale factors, level
+    # counts and FAST thresholds (exercise the byte-wise copy path, the partial last column group of the resize,
+    # wider source windows, other cell grids)
+    "odd641": (641, 481, 12, (800, 1.2, 6, 20, 7), [(0, 0), (100, 300)]),
+    "scale11": (503, 377, 13, (900, 1.1, 8, 25, 9), [(0, 0)]),
+    "scale15": (701, 499, 14, (700, 1.5, 4, 30, 10), [(0, 350)]),
+    "one_level": (322, 242, 15, (400, 1.2, 1, 20, 7), [(0, 0)]),
+    "tall": (300, 500, 16, (500, 1.25, 5, 15, 5), [(0, 0)]),
 }
 
 
@@ -97,6 +105,32 @@ def test_extractor_matches_cv2_goldens(name):
         c = ex.fast_candidates(l)
         got = np.stack([c["x"], c["y"], c["response"]], 1).astype(np.int32).reshape(-1, 3)
         assert np.array_equal(got, g["cand%d" % l]), "FAST candidates level %d" % l
+    ex.close()
+
+
+@pytest.mark.parametrize("pattern", ["dots", "checker", "stripes_noise"])
+def test_regular_patterns_stress_ties(pattern):
+    """Regular images produce many corners with equal scores (NMS ties: equal neighbours suppress each other) and many
+    quadtree nodes of equal size (the creation-order tie-break and the partial rounds decide who survives)."""
+    W, H, params = 640, 480, (1000, 1.2, 8, 20, 7)
+    yy, xx = np.mgrid[0:H, 0:W]
+    if pattern == "dots":
+        img = np.where(((xx % 12) < 3) & ((yy % 12) < 3), 220, 40).astype(np.uint8)
+    elif pattern == "checker":
+        img = np.where(((xx // 16) + (yy // 16)) % 2 == 0, 200, 60).astype(np.uint8)
+    else:
+        rng = np.random.RandomState(5)
+        img = (np.where((xx // 9) % 2 == 0, 180, 70) + rng.randint(-12, 13, (H, W))).clip(0, 255).astype(np.uint8)
+    ex = ORBextractor(*params, width=W, height=H)
+    orc = O.OracleExtractor(*params)
+    for lap in [(0, 0), (0, 1000)]:
+        mono, kps, desc = ex(img, lap)
+        omono, okps, odesc = orc(img, lap)
+        assert mono == omono
+        assert_same_keypoints(kps, okps, "%s lap %s" % (pattern, lap))
+        assert np.array_equal(desc, odesc)
+    compare_stages(ex, orc, params[2])
+    assert len(kps) > 300
     ex.close()
 
 
