@@ -1,7 +1,9 @@
 #!/usr/bin/env python3
 """Print the interesting fields of bench.py's JSON line (development aid): python bench.py ... | python tools/show_bench.py"""
 import json
+import signal
 import sys
+signal.signal(signal.SIGPIPE, signal.SIG_DFL)
 for l in sys.stdin:
     if not l.startswith("{"):
         print(l.rstrip()[:300])
