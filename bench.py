@@ -287,7 +287,7 @@ def main():
     except (OSError, KeyError, ValueError):
         pass
     stage_kernels = {"pyramid": "k_pyramid_copy0 + 7 x k_pyramid_level + k_pyramid_borders",
-                     "fast": "k_fast_stream + k_fast_nms + k_fast_cells_list", "blur": "8 x k_blur7", "quadtree": "k_quadtree",
+                     "fast": "k_fast_stream + k_fast_nms + k_fast_cells_list", "blur": "k_blur7 (all levels in one launch)", "quadtree": "k_quadtree",
                      "assemble": "k_assemble", "orient_describe": "k_orient_describe"}
     roofline = {"bound": "hbm", "kernel": STAGES[top], "kernels": stage_kernels.get(STAGES[top]), "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": achieved / peak, "traffic": traffic,
@@ -411,7 +411,7 @@ def main():
                            "mean_keypoints_per_frame": nkp, "parallelism": "frames sharded by rank, no collective"},
                 "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
                 "single_frame_latency_ms": single_ms,
-                "gpu_launches": (2 * (2 * PARAMS[2] + 7) + 3) * args.steps,
+                "gpu_launches": (2 * (PARAMS[2] + 8) + 3) * args.steps,
                 "hamming": hamming}
         print(json.dumps(line), flush=True)
     if world > 1:

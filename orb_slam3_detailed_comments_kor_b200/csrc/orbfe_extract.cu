@@ -178,11 +178,17 @@ __global__ void __launch_bounds__(256) k_pyramid_borders(const __grid_constant__
 #define BLUR_TW 64
 #define BLUR_TH 56
 #define BLUR_PAIRS (BLUR_TH / 2 + 4)   /* tile rows y0-4 .. y0+TH+3 as pairs */
-__global__ void __launch_bounds__(256) k_blur7(const __grid_constant__ ExDesc d, ExBuffers b, int level) {
+__global__ void __launch_bounds__(256) k_blur7(const __grid_constant__ ExDesc d, ExBuffers b) {
     __shared__ __align__(16) uint32_t s_h[BLUR_PAIRS][BLUR_TW];
+    /* one launch covers every level: blockIdx.x walks the 64x56 tiles of level 0, then level 1, ... (d.blurTile0[l] =
+     * first tile of level l) */
+    int level = 0;
+    while (level + 1 < d.nlevels && (int)blockIdx.x >= d.blurTile0[level + 1]) level++;
     const LevelDesc& L = d.lv[level];
-    const size_t f = blockIdx.z;
-    const int x0 = blockIdx.x * BLUR_TW, y0 = blockIdx.y * BLUR_TH;
+    const size_t f = blockIdx.y;
+    const int tilesX = (L.w + BLUR_TW - 1) / BLUR_TW, tile = blockIdx.x - d.blurTile0[level];
+    const int ty = tile / tilesX, tx = tile - ty * tilesX;
+    const int x0 = tx * BLUR_TW, y0 = ty * BLUR_TH;
     const uint8_t* pad = b.pyr + f * d.pyrSlab + L.pyrOff + ORBFE_ROW_LEAD + x0 - 4;
     const uint32_t KLO = 18u | (34u << 8) | (48u << 16) | (56u << 24);  /* taps -3..0 */
     const uint32_t KHI = 48u | (34u << 8) | (18u << 16);                /* taps +1..+3 */
@@ -1234,6 +1240,8 @@ int orbfe_quadtree_smem_bytes(int cap) {
 
 int orbfe_collect_stage_times(orbfe_extractor* ex);
 
+int orbfe_blur_tiles(int w, int h) { return ((w + BLUR_TW - 1) / BLUR_TW) * ((h + BLUR_TH - 1) / BLUR_TH); }
+
 int orbfe_configure_kernels(int quadSmem, int fastSmem) {
     ORBFE_CUDA(cudaFuncSetAttribute(k_quadtree, cudaFuncAttributeMaxDynamicSharedMemorySize, quadSmem));
     ORBFE_CUDA(cudaFuncSetAttribute(k_fast_cells_list, cudaFuncAttributeMaxDynamicSharedMemorySize, fastSmem));
@@ -1283,10 +1291,7 @@ int orbfe_launch_extract(orbfe_extractor* ex, const uint8_t* d_images, int nfram
     k_fast_nms<<<dim3((d.nCells + FN_WARPS - 1) / FN_WARPS, nframes), FN_WARPS * 32, 0, st>>>(d, xb);
     k_fast_cells_list<<<148 * 8, FAST_NT, ex->fastSmem, st>>>(d, xb);
     STAGE_MARK();
-    for (int l = 0; l < d.nlevels; l++) {
-        const LevelDesc& L = d.lv[l];
-        k_blur7<<<dim3((L.w + BLUR_TW - 1) / BLUR_TW, (L.h + BLUR_TH - 1) / BLUR_TH, nframes), 256, 0, st>>>(d, xb, l);
-    }
+    k_blur7<<<dim3(d.blurTile0[d.nlevels], nframes), 256, 0, st>>>(d, xb);
     STAGE_MARK();
     k_quadtree<<<dim3(d.nlevels, nframes), QT_NT, ex->quadSmem, st>>>(d, xb);
     STAGE_MARK();
@@ -1296,7 +1301,7 @@ int orbfe_launch_extract(orbfe_extractor* ex, const uint8_t* d_images, int nfram
     STAGE_MARK();
 #undef STAGE_MARK
     if (prof) ex->stagePending = 1;
-    ex->launches += 2 * d.nlevels + 6 + (d.nlevels > 1 ? 1 : 0);
+    ex->launches += d.nlevels + 7 + (d.nlevels > 1 ? 1 : 0);
     ORBFE_CUDA(cudaGetLastError());
     return 0;
 }

@@ -15,6 +15,7 @@
 int orbfe_upload_constants(const int* umax16, const int8_t* pattern1024);
 int orbfe_quadtree_smem_bytes(int cap);
 int orbfe_configure_kernels(int quadSmem, int fastSmem);
+int orbfe_blur_tiles(int w, int h);
 int orbfe_launch_extract(orbfe_extractor* ex, const uint8_t* d_images, int nframes, int lap0, int lap1, cudaStream_t st, int frame0);
 int orbfe_collect_stage_times(orbfe_extractor* ex);
 
@@ -276,6 +277,8 @@ int orbfe_extractor_create(const orbfe_params* p, int device, int width, int hei
     d.nCells = (int)cells.size();
     d.candCap = keyTotal;
     d.nStrips = (int)strips.size();
+    d.blurTile0[0] = 0;
+    for (int l = 0; l < nl; l++) d.blurTile0[l + 1] = d.blurTile0[l] + orbfe_blur_tiles(d.lv[l].w, d.lv[l].h);
     d.stBands = (height >> 3) + 1;
     d.rawCap = rawTotal;
     d.kpCap = selTotal;

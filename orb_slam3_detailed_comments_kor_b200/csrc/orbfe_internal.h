@@ -47,6 +47,7 @@ struct ExDesc {
     int kpCap;        /* selected keypoints per frame, all levels (= sum selCap) */
     int nodeCap;      /* quadtree node capacity (max over levels of selCap, padded) */
     int iniTh, minTh;
+    int blurTile0[ORBFE_MAX_LEVELS + 1]; /* first blur tile of each level in the one blur launch; [nlevels] = total */
     int stBands;      /* 8-row bands of the stereo candidate table: (H >> 3) + 1 */
     int nStrips;      /* strips of k_fast_stream per frame */
     int rawCap;       /* raw-corner slots per frame */
