@@ -546,7 +546,7 @@ __global__ void __launch_bounds__(FAST_NT, 8) k_fast_cells_list(const __grid_con
  * k_fast_nms then does the cell-local non-maximum suppression and ordering. */
 #define FS_BROWS (FS_R + 6)   /* rows yc-3 .. yc+FS_R+2 of the current chunk */
 #define FS_PW 33               /* words per buffered row: 32 + 1 so that equal columns of different rows hit different banks */
-__global__ void __launch_bounds__(FS_WARPS * 32, 8) k_fast_stream(const __grid_constant__ ExDesc d, ExBuffers b) {
+__global__ void __launch_bounds__(FS_WARPS * 32, 8) k_fast_stream(const __grid_constant__ ExDesc d, ExBuffers b, int stripBase, int nStrips) {
     __shared__ __align__(16) uint32_t s_buf[FS_WARPS][FS_BROWS][FS_PW];
     __shared__ uint32_t s_hits[FS_WARPS][FS_R][32];
     __shared__ uint16_t s_q[FS_WARPS][FS_R * FS_COLS + 32];
@@ -554,8 +554,8 @@ __global__ void __launch_bounds__(FS_WARPS * 32, 8) k_fast_stream(const __grid_c
     const size_t f = blockIdx.y;
     if (blockIdx.x == 0 && threadIdx.x == 0 && f == 0) *b.fbCount = 0; /* list of empty cells restarts every batch */
     const int sidx = blockIdx.x * FS_WARPS + warp;
-    if (sidx >= d.nStrips) return;
-    const StripDesc sd = b.strips[sidx];
+    if (sidx >= nStrips) return;
+    const StripDesc sd = b.strips[stripBase + sidx];
     const LevelDesc& L = d.lv[sd.level];
     const int pitch = L.pitch, th = d.iniTh;
     const int col = sd.xs - 4 + 4 * lane;                       /* level x of my word's byte 0 */
@@ -1287,7 +1287,11 @@ int orbfe_launch_extract(orbfe_extractor* ex, const uint8_t* d_images, int nfram
     }
     if (d.nlevels > 1) k_pyramid_borders<<<dim3((maxBorder + 255) / 256, d.nlevels - 1, nframes), 256, 0, st>>>(d, xb);
     STAGE_MARK();
-    k_fast_stream<<<dim3((d.nStrips + FS_WARPS - 1) / FS_WARPS, nframes), FS_WARPS * 32, 0, st>>>(d, xb);
+    {
+        const bool few = nframes < 8;   /* few frames: the 16-row cut puts three times as many warps in flight */
+        const int sb = few ? d.nStrips : 0, sn = few ? d.nStripsShort : d.nStrips;
+        k_fast_stream<<<dim3((sn + FS_WARPS - 1) / FS_WARPS, nframes), FS_WARPS * 32, 0, st>>>(d, xb, sb, sn);
+    }
     k_fast_nms<<<dim3((d.nCells + FN_WARPS - 1) / FN_WARPS, nframes), FN_WARPS * 32, 0, st>>>(d, xb);
     k_fast_cells_list<<<148 * 8, FAST_NT, ex->fastSmem, st>>>(d, xb);
     STAGE_MARK();

@@ -164,7 +164,7 @@ int orbfe_extractor_create(const orbfe_params* p, int device, int width, int hei
     ExDesc& d = ex->d;
     d.nlevels = nl; d.W = width; d.H = height; d.iniTh = p->ini_th_fast; d.minTh = p->min_th_fast;
     std::vector<CellDesc> cells;
-    std::vector<StripDesc> strips;
+    std::vector<StripDesc> strips, stripsShort;
     int rawTotal = 0;
     std::vector<uint2> tabs;
     size_t pyrOff = 0, blurOff = 0;
@@ -241,13 +241,19 @@ int orbfe_extractor_create(const orbfe_params* p, int device, int width, int hei
         L.rawBase = rawTotal;
         L.rawStride = L.wCell * L.hCell;
         rawTotal += L.nCols * L.nRows * L.rawStride;
-        for (int y0 = ORBFE_EDGE; y0 < L.h - ORBFE_EDGE; y0 += 48)
-            for (int xs = ORBFE_MIN_BORDER; xs < L.w - ORBFE_EDGE; xs += 120) {
-                StripDesc sd;
-                sd.level = (short)l; sd.xs = (short)xs; sd.y0 = (short)y0;
-                sd.nrows = (short)std::min(48, L.h - ORBFE_EDGE - y0);
-                strips.push_back(sd);
-            }
+        /* two cuts of the level into strips: 48 rows (batches: less preload overhead) and 16 rows (a few frames: three
+           times as many warps in flight, lower latency) */
+        for (int cut = 0; cut < 2; cut++) {
+            const int sh = cut ? 16 : 48;
+            std::vector<StripDesc>& dst = cut ? stripsShort : strips;
+            for (int y0 = ORBFE_EDGE; y0 < L.h - ORBFE_EDGE; y0 += sh)
+                for (int xs = ORBFE_MIN_BORDER; xs < L.w - ORBFE_EDGE; xs += 120) {
+                    StripDesc sd;
+                    sd.level = (short)l; sd.xs = (short)xs; sd.y0 = (short)y0;
+                    sd.nrows = (short)std::min(sh, L.h - ORBFE_EDGE - y0);
+                    dst.push_back(sd);
+                }
+        }
         nodeCap = std::max(nodeCap, std::max(L.selCap, std::max(L.nIni, L.nCols * L.nRows)));
         if (l > 0) {
             while (tabs.size() % 4) tabs.push_back(make_uint2(0, 0)); /* k_pyramid_level reads tabX four entries at a time */
@@ -277,6 +283,7 @@ int orbfe_extractor_create(const orbfe_params* p, int device, int width, int hei
     d.nCells = (int)cells.size();
     d.candCap = keyTotal;
     d.nStrips = (int)strips.size();
+    d.nStripsShort = (int)stripsShort.size();
     d.blurTile0[0] = 0;
     for (int l = 0; l < nl; l++) d.blurTile0[l + 1] = d.blurTile0[l] + orbfe_blur_tiles(d.lv[l].w, d.lv[l].h);
     d.stBands = (height >> 3) + 1;
@@ -333,7 +340,7 @@ int orbfe_extractor_create(const orbfe_params* p, int device, int width, int hei
     TRY(dev_alloc(ex, &b.stTable, B * d.kpCap));
     TRY(dev_alloc(ex, &b.stBand, B * (d.stBands + 1)));
     TRY(dev_alloc(ex, &dCells, cells.size()));
-    TRY(dev_alloc(ex, &dStrips, strips.size()));
+    TRY(dev_alloc(ex, &dStrips, strips.size() + stripsShort.size()));
     TRY(dev_alloc(ex, &b.raw, B * (size_t)d.rawCap));
     TRY(dev_alloc(ex, &b.rawCount, B * d.nCells));
     TRY(dev_alloc(ex, &b.fbList, B * d.nCells));
@@ -343,6 +350,7 @@ int orbfe_extractor_create(const orbfe_params* p, int device, int width, int hei
     b.cells = dCells;
     b.strips = dStrips;
     TRYC(cudaMemcpy(dStrips, strips.data(), strips.size() * sizeof(StripDesc), cudaMemcpyHostToDevice));
+    TRYC(cudaMemcpy(dStrips + strips.size(), stripsShort.data(), stripsShort.size() * sizeof(StripDesc), cudaMemcpyHostToDevice));
     TRYC(cudaMemset(b.rawCount, 0, B * d.nCells * sizeof(int)));
     TRYC(cudaMemset(b.fbCount, 0, sizeof(int)));
     b.tabs = dTabs;
