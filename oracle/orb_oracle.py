@@ -195,3 +195,24 @@ def knn2_ratio(q, t, ratio=0.7):
     d1 = np.zeros(q.shape[0], np.int32)
     lib().orc_knn2_ratio(_ptr(q), q.shape[0], _ptr(t), t.shape[0], ratio, _ptr(m), _ptr(d0), _ptr(d1))
     return m, d0, d1
+
+
+def merge_top2_host(parts, th, ratio, strict_lt):
+    """Oracle of the shard merge (k_top2_merge / orbfe_top2_merge_device): parts is [nshards, nq] MATCH_DTYPE in ascending
+    shard (= global row) order; scanning the shards in that order with the reference's strict `<` update
+    (src/ORBmatcher.cc:330-340) gives what one scan over the whole database gives."""
+    parts = np.asarray(parts)
+    ns, nq = parts.shape
+    out = np.zeros(nq, MATCH_DTYPE)
+    b1 = np.full(nq, 256, np.int32); b2 = b1.copy(); bi = np.full(nq, -1, np.int32)
+    for s in range(ns):
+        d1, d2, ix = parts[s]["best1"], parts[s]["best2"], parts[s]["idx"]
+        lt = d1 < b1
+        b2 = np.where(lt, b1, np.where(d1 < b2, d1, b2))
+        bi = np.where(lt, ix, bi)
+        b1 = np.where(lt, d1, b1)
+        b2 = np.minimum(b2, d2)
+    out["best1"], out["best2"], out["idx"] = b1, b2, bi
+    th_ok = (b1 < th) if strict_lt else (b1 <= th)
+    out["accepted"] = th_ok & (b1.astype(np.float32) < np.float32(ratio) * b2.astype(np.float32))
+    return out

@@ -84,26 +84,6 @@ def merge_top2_device(device, d_parts, nshards, nq, th, ratio, strict_lt, d_out,
                                              C.c_void_p(d_out), C.c_void_p(stream) if stream else None))
 
 
-def merge_top2_host(parts, th, ratio, strict_lt):
-    """Host statement of the shard merge (used by the gloo CPU tests of the multi-rank plumbing; same rule as
-    k_top2_merge): parts is [nshards, nq] MATCH_DTYPE in ascending shard (= global row) order."""
-    parts = np.asarray(parts)
-    ns, nq = parts.shape
-    out = np.zeros(nq, MATCH_DTYPE)
-    b1 = np.full(nq, 256, np.int32); b2 = b1.copy(); bi = np.full(nq, -1, np.int32)
-    for s in range(ns):
-        d1, d2, ix = parts[s]["best1"], parts[s]["best2"], parts[s]["idx"]
-        lt = d1 < b1
-        b2 = np.where(lt, b1, np.where(d1 < b2, d1, b2))
-        bi = np.where(lt, ix, bi)
-        b1 = np.where(lt, d1, b1)
-        b2 = np.minimum(b2, d2)
-    out["best1"], out["best2"], out["idx"] = b1, b2, bi
-    th_ok = (b1 < th) if strict_lt else (b1 <= th)
-    out["accepted"] = th_ok & (b1.astype(np.float32) < np.float32(ratio) * b2.astype(np.float32))
-    return out
-
-
 def compute_stereo_matches(exL, exR, nframes, mbf, minD, maxD, stream=None):
     """Frame::ComputeStereoMatches on the frames exL/exR extracted last (device resident)."""
     check(_lib.lib().orbfe_stereo_match_batch_device(exL.handle, exR.handle, nframes, mbf, minD, maxD,

@@ -3,11 +3,8 @@
 * Frames / stereo pairs are independent: rank r processes pairs r, r+R, ... with its own extractors — no collective.
 * The map-descriptor database is split into R contiguous row ranges; every rank searches its range with
   index_base = first global row, the per-shard top-2 records are all-gathered (NCCL on GPUs, gloo in the CPU tests)
-  and merged with the same strict-< rule a single scan applies (k_top2_merge / merge_top2_host).
+  and merged on the GPU with the same strict-< rule a single scan applies (k_top2_merge).
 The reference is single-process (SURVEY.md §5 'Distributed communication backend: none'); this file is new."""
-import numpy as np
-
-from ._lib import MATCH_DTYPE
 
 
 def shard_rows(ndb, world, rank):
@@ -35,15 +32,14 @@ def gather_top2(local, world, group=None):
 
 
 def merge_gathered(gathered, th, ratio, strict_lt, device=None, stream=None):
-    """Merge [world, nq, 4] per-shard records.  CUDA tensors go through k_top2_merge (orbfe_top2_merge_device),
-    CPU tensors through the host statement of the same rule (used by the gloo tests)."""
+    """Merge [world, nq, 4] per-shard records on the GPU (k_top2_merge via orbfe_top2_merge_device).  There is no CPU
+    path: a host tensor is an error."""
     import torch
     from . import matcher as M
     world, nq = gathered.shape[0], gathered.shape[1]
-    if gathered.is_cuda:
-        out = torch.empty((nq, 4), dtype=torch.int32, device=gathered.device)
-        M.merge_top2_device(gathered.device.index if device is None else device, gathered.data_ptr(), world, nq, th, ratio,
-                            strict_lt, out.data_ptr(), stream)
-        return out
-    parts = gathered.numpy().view(MATCH_DTYPE).reshape(world, nq)
-    return torch.from_numpy(M.merge_top2_host(parts, th, ratio, strict_lt).view(np.int32).reshape(nq, 4))
+    if not gathered.is_cuda:
+        raise RuntimeError("merge_gathered needs CUDA tensors: the product has no CPU path")
+    out = torch.empty((nq, 4), dtype=torch.int32, device=gathered.device)
+    M.merge_top2_device(gathered.device.index if device is None else device, gathered.data_ptr(), world, nq, th, ratio,
+                        strict_lt, out.data_ptr(), stream)
+    return out

@@ -8,7 +8,7 @@ import numpy as np
 import pytest
 
 from orb_slam3_detailed_comments_kor_b200 import _lib
-from orb_slam3_detailed_comments_kor_b200.matcher import merge_top2_host
+from oracle.orb_oracle import merge_top2_host
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
@@ -42,6 +42,15 @@ def test_no_cpu_fallback_without_gpu():
 
 def test_keypoint_layout_is_cv_keypoint():
     assert _lib.KP_DTYPE.itemsize == 28 and _lib.MATCH_DTYPE.itemsize == 16
+
+
+def test_product_package_never_touches_the_oracle():
+    import glob
+    pkg = os.path.join(ROOT, "orb_slam3_detailed_comments_kor_b200")
+    for path in glob.glob(os.path.join(pkg, "**", "*"), recursive=True):
+        if path.endswith((".py", ".cu", ".cuh", ".h", ".cpp")):
+            text = open(path, errors="ignore").read()
+            assert "orb_oracle" not in text and "liborb_oracle" not in text and "from oracle" not in text, path
 
 
 def test_host_merge_rule():

@@ -308,7 +308,7 @@ def test_top2_full_size_properties_and_sharding():
     merged = d_out.cpu().numpy()
     assert np.array_equal(merged[:, 0], full["best1"]) and np.array_equal(merged[:, 1], full["best2"])
     assert np.array_equal(merged[:, 2], full["idx"]) and np.array_equal(merged[:, 3], full["accepted"])
-    host = M.merge_top2_host(d_parts.cpu().numpy().view(M.MATCH_DTYPE).reshape(shards, nq), 50, 0.9, False)
+    host = O.merge_top2_host(d_parts.cpu().numpy().view(O.MATCH_DTYPE).reshape(shards, nq), 50, 0.9, False)
     assert np.array_equal(host["idx"], full["idx"]) and np.array_equal(host["accepted"], full["accepted"])
 
 

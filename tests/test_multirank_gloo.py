@@ -1,6 +1,7 @@
-"""world_size-2 gloo tests (CPU) of the multi-rank host logic: database sharding + all-gather + merge gives the
-single-scan answer, and frame sharding covers every frame exactly once.  The per-shard searches here are done by the
-CPU oracle (test infrastructure); on GPUs the same plumbing runs over NCCL with k_top2_partial / k_top2_merge."""
+"""world_size-2 gloo tests (CPU) of the multi-rank host logic: database sharding + all-gather gives every rank all shards'
+records in global-row order, merging them gives the single-scan answer, and frame sharding covers every frame exactly
+once.  The per-shard searches and the merge are done here by the CPU oracle (test infrastructure); on GPUs the same
+plumbing runs over NCCL with k_top2_partial / k_top2_merge (tests/test_gpu_parity.py checks those against the oracle)."""
 import os
 import socket
 
@@ -37,7 +38,8 @@ def _worker(rank, world, port, ndb, nq, strict, ret):
     part["idx"] = np.where(part["idx"] >= 0, part["idx"] + lo, -1)
     local = torch.from_numpy(part.view(np.int32).reshape(nq, 4).copy())
     gathered = sharding.gather_top2(local, world)
-    merged = sharding.merge_gathered(gathered, 50, 0.9, strict).numpy()
+    parts = gathered.numpy().view(O.MATCH_DTYPE).reshape(world, nq)          # gathered in rank order
+    merged = O.merge_top2_host(parts, 50, 0.9, strict).view(np.int32).reshape(nq, 4)   # the merge rule's oracle (on GPUs: k_top2_merge)
     whole = O.hamming_top2(q, db, 50, 0.9, strict).view(np.int32).reshape(nq, 4)
     frames = sharding.frames_for_rank(11, world, rank)
     allf = [None] * world
