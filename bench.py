@@ -352,6 +352,26 @@ def main():
     single_ms = (time.perf_counter() - t0) * 1e3 / 20
     ex1.close()
 
+    # ---- input conditioning: rectification of the same frames, device to device
+    from orb_slam3_detailed_comments_kor_b200.conditioning import Rectifier
+    yy, xx = np.mgrid[0:H, 0:W].astype(np.float32)
+    xn, yn = (xx - 367.215) / 458.654, (yy - 248.375) / 457.296            # EuRoC cam0 intrinsics / distortion (EuRoC.yaml)
+    r2 = xn * xn + yn * yn
+    fac = (1 - 0.28340811 * r2 + 0.07395907 * r2 * r2).astype(np.float32)
+    rect = Rectifier((xn * fac * 458.654 + 367.215).astype(np.float32), (yn * fac * 457.296 + 248.375).astype(np.float32), device=local_rank)
+    d_rect = torch.empty_like(dL)
+    for _ in range(3):
+        rect.batch_device(dL.data_ptr(), d_rect.data_ptr(), P, st)
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        rect.batch_device(dL.data_ptr(), d_rect.data_ptr(), P, st)
+    e1.record()
+    barrier()
+    rect_ms = max_over_ranks(e0.elapsed_time(e1) / args.steps)
+    rectify = {"value": P * world / (rect_ms / 1e3), "unit": "frames/s", "ms_per_step": rect_ms, "frames_per_step": P * world,
+               "achieved_gbs": P * W * H * 2 / (rect_ms / 1e3) / 1e9, "note": "cv::remap INTER_LINEAR, read + write of the frame counted"}
+
     # ---- Hamming top-2 (config 5): database sharded over the ranks, NCCL all-gather of the per-shard top-2 + merge
     from orb_slam3_detailed_comments_kor_b200 import sharding
     nq, ndb = args.hamming_queries, args.hamming_db
@@ -410,7 +430,7 @@ def main():
                            "l2": "inputs_larger_than_L2 (%d MB of images per step per GPU)" % (2 * P * W * H >> 20),
                            "mean_keypoints_per_frame": nkp, "parallelism": "frames sharded by rank, no collective"},
                 "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
-                "single_frame_latency_ms": single_ms,
+                "single_frame_latency_ms": single_ms, "rectify": rectify,
                 "gpu_launches": (2 * (PARAMS[2] + 8) + 3) * args.steps,
                 "hamming": hamming}
         print(json.dumps(line), flush=True)

@@ -183,6 +183,27 @@ int orbfe_hamming_top2(int device, const uint8_t* q, int nq, const uint8_t* db, 
 int orbfe_knn2_ratio(int device, const uint8_t* q, int nq, const uint8_t* t, int nt, double ratio, int32_t* match,
                      int32_t* d0, int32_t* d1);
 
+/* ------------------------------------------------------------------------------------------ input conditioning */
+/* The steps the example drivers and Tracking run on each image before the extractor, so that an
+ * uploaded frame can stay on the GPU.  Bit-exact with OpenCV 4.13's 8-bit fixed-point paths. */
+typedef struct orbfe_rectifier orbfe_rectifier;
+
+/* Replaces cv::remap(im, imRect, M1, M2, cv::INTER_LINEAR) (Examples/Stereo-Inertial/stereo_inertial_euroc.cc:201-202; also the
+ * other stereo drivers) for CV_32FC1 maps as produced by cv::initUndistortRectifyMap(..., CV_32F, M1, M2) (:150-151).
+ * map_x / map_y: width*height floats on the host, converted once to OpenCV's 5-bit fixed point.  Border: constant 0. */
+int orbfe_rectifier_create(int device, int width, int height, const float* map_x, const float* map_y, orbfe_rectifier** out);
+void orbfe_rectifier_destroy(orbfe_rectifier* r);
+/* nframes dense width*height u8 frames, device to device (may feed orbfe_extract_batch_device); asynchronous on `stream`. */
+int orbfe_rectify_batch_device(orbfe_rectifier* r, const uint8_t* d_src, uint8_t* d_dst, int nframes, void* stream);
+/* one host image in, one host image out (steps in bytes); synchronous */
+int orbfe_rectify(orbfe_rectifier* r, const uint8_t* src, size_t sstep, uint8_t* dst, size_t dstep);
+
+/* Replaces cvtColor(im, gray, cv::COLOR_RGB2GRAY / BGR2GRAY / RGBA2GRAY / BGRA2GRAY) of Tracking::GrabImageStereo / RGBD /
+ * Monocular (src/Tracking.cc:1303-1328, 1360-1372, 1399-1411).  channels = 3 or 4 (interleaved), rgb_order != 0 when the first
+ * channel is red (mbRGB).  Device to device, asynchronous on `stream` (NULL = default stream). */
+int orbfe_to_gray_device(int device, const uint8_t* d_src, int channels, int rgb_order, int width, int height, int nframes,
+                         uint8_t* d_dst, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -19,7 +19,7 @@ MATCH_DTYPE = np.dtype([("best1", "<i4"), ("best2", "<i4"), ("idx", "<i4"), ("ac
 
 def build(force=False):
     """Compile the oracle with its Makefile (gcc only; no reference sources are read)."""
-    srcs = [os.path.join(_HERE, f) for f in ("orb_oracle.cpp", "match_oracle.cpp", "orb_oracle.h", "Makefile")]
+    srcs = [os.path.join(_HERE, f) for f in ("orb_oracle.cpp", "match_oracle.cpp", "condition_oracle.cpp", "orb_oracle.h", "Makefile")]
     if force or not os.path.exists(_SO) or any(os.path.getmtime(s) > os.path.getmtime(_SO) for s in srcs):
         subprocess.check_call(["make", "-C", _HERE, "liborb_oracle.so"], stdout=subprocess.DEVNULL)
     return _SO
@@ -60,6 +60,8 @@ def lib():
     L.orc_stereo_match.restype = C.c_int
     L.orc_stereo_match.argtypes = [vp, vp, vp, vp, C.c_int, vp, vp, C.c_int, C.c_float, C.c_float, C.c_float, vp, vp]
     L.orc_knn2_ratio.argtypes = [vp, C.c_int, vp, C.c_int, C.c_double, vp, vp, vp]
+    L.orc_remap_linear_u8.argtypes = [vp, C.c_int, C.c_int, C.c_int, vp, vp, vp, C.c_int]
+    L.orc_to_gray.argtypes = [vp, C.c_longlong, C.c_int, C.c_int, vp]
     _lib = L
     return L
 
@@ -195,6 +197,23 @@ def knn2_ratio(q, t, ratio=0.7):
     d1 = np.zeros(q.shape[0], np.int32)
     lib().orc_knn2_ratio(_ptr(q), q.shape[0], _ptr(t), t.shape[0], ratio, _ptr(m), _ptr(d0), _ptr(d1))
     return m, d0, d1
+
+
+def remap_linear(src, mapx, mapy):
+    """cv::remap(src, dst, mapx, mapy, INTER_LINEAR), 8UC1, float maps, constant-0 border."""
+    src = np.ascontiguousarray(src, np.uint8)
+    mx = np.ascontiguousarray(mapx, np.float32); my = np.ascontiguousarray(mapy, np.float32)
+    dst = np.zeros_like(src)
+    lib().orc_remap_linear_u8(_ptr(src), src.shape[1], src.shape[0], src.shape[1], _ptr(mx), _ptr(my), _ptr(dst), src.shape[1])
+    return dst
+
+
+def to_gray(img, rgb):
+    """cv::cvtColor(img, COLOR_{RGB,BGR,RGBA,BGRA}2GRAY); img is [h, w, 3 or 4] u8, rgb = first channel is red."""
+    img = np.ascontiguousarray(img, np.uint8)
+    dst = np.zeros(img.shape[:2], np.uint8)
+    lib().orc_to_gray(_ptr(img), img.shape[0] * img.shape[1], img.shape[2], int(rgb), _ptr(dst))
+    return dst
 
 
 def merge_top2_host(parts, th, ratio, strict_lt):

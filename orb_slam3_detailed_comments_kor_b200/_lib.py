@@ -66,6 +66,11 @@ SIGNATURES = {
     "orbfe_top2_merge_device": (i32, [i32, vp, i32, i32, i32, f32, i32, vp, vp]),
     "orbfe_hamming_top2_static": (i32, [i32, vp, i32, vp, i64, i64, i32, f32, i32, vp, vp]),
     "orbfe_hamming_top2": (i32, [i32, vp, i32, vp, i64, i32, f32, i32, vp]),
+    "orbfe_rectifier_create": (i32, [i32, i32, i32, vp, vp, C.POINTER(vp)]),
+    "orbfe_rectifier_destroy": (None, [vp]),
+    "orbfe_rectify_batch_device": (i32, [vp, vp, vp, i32, vp]),
+    "orbfe_rectify": (i32, [vp, vp, sz, vp, sz]),
+    "orbfe_to_gray_device": (i32, [i32, vp, i32, i32, i32, i32, i32, vp, vp]),
     "orbfe_knn2_ratio": (i32, [i32, vp, i32, vp, i32, f64, vp, vp, vp]),
 }
 

@@ -445,6 +445,27 @@ def main():
     prim["atan_yx"] = yx
     prim["atan_out"] = np.array([cv2.fastAtan2(float(y), float(x)) for y, x in yx], f32)
     np.savez_compressed(os.path.join(out_dir, "primitives.npz"), **prim)
+
+    # input conditioning: cv2.remap (float maps, INTER_LINEAR) and cv2.cvtColor to gray
+    cond = {}
+    H, W = 120, 163
+    src = rng.randint(0, 256, (H, W)).astype(np.uint8)
+    yy, xx = np.mgrid[0:H, 0:W].astype(f32)
+    k1, k2 = f32(-0.28), f32(0.07)                        # a radial-distortion-like map plus jitter; parts fall outside the image
+    xn, yn = (xx - f32(W / 2)) / f32(140), (yy - f32(H / 2)) / f32(140)
+    r2 = xn * xn + yn * yn
+    fac = f32(1) + k1 * r2 + k2 * r2 * r2
+    cond["src"] = src
+    cond["mapx"] = (xn * fac * f32(158) + f32(W / 2) + f32(7.3) + rng.uniform(-0.4, 0.4, (H, W))).astype(f32)
+    cond["mapy"] = (yn * fac * f32(158) + f32(H / 2) - f32(5.7) + rng.uniform(-0.4, 0.4, (H, W))).astype(f32)
+    cond["remap_out"] = cv2.remap(src, cond["mapx"], cond["mapy"], cv2.INTER_LINEAR)
+    col = rng.randint(0, 256, (61, 83, 4)).astype(np.uint8)
+    cond["color"] = col
+    cond["gray_rgb"] = cv2.cvtColor(np.ascontiguousarray(col[..., :3]), cv2.COLOR_RGB2GRAY)
+    cond["gray_bgr"] = cv2.cvtColor(np.ascontiguousarray(col[..., :3]), cv2.COLOR_BGR2GRAY)
+    cond["gray_rgba"] = cv2.cvtColor(col, cv2.COLOR_RGBA2GRAY)
+    cond["gray_bgra"] = cv2.cvtColor(col, cv2.COLOR_BGRA2GRAY)
+    np.savez_compressed(os.path.join(out_dir, "conditioning.npz"), **cond)
     print("wrote goldens to", out_dir, "cv2", cv2.__version__)
 
 
