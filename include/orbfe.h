@@ -204,6 +204,22 @@ int orbfe_rectify(orbfe_rectifier* r, const uint8_t* src, size_t sstep, uint8_t*
 int orbfe_to_gray_device(int device, const uint8_t* d_src, int channels, int rgb_order, int width, int height, int nframes,
                          uint8_t* d_dst, void* stream);
 
+/* Replaces cv::createCLAHE(clip_limit, cv::Size(tiles_x, tiles_y)) + clahe->apply(im, im) of the TUM-VI drivers
+ * (Examples/Stereo-Inertial/stereo_inertial_tum_vi.cc:128 and :137-138; also Examples/Stereo/stereo_tum_vi.cc,
+ * Examples/Monocular/mono_tum_vi.cc, Examples/Monocular-Inertial/mono_inertial_tum_vi.cc: clip 3.0, 8 x 8 tiles).  8-bit single
+ * channel; sizes that do not divide by the grid follow OpenCV (REFLECT_101 extension for the histograms).
+ * ORBFE_E_INVALID when the image is smaller than that extension.  max_batch sizes the per-frame lut storage. */
+typedef struct orbfe_clahe orbfe_clahe;
+int orbfe_clahe_create(int device, int width, int height, double clip_limit, int tiles_x, int tiles_y, int max_batch, orbfe_clahe** out);
+void orbfe_clahe_destroy(orbfe_clahe* c);
+/* nframes dense width*height u8 frames, device to device; d_dst may equal d_src (the reference applies in place).  Asynchronous on
+ * `stream` (NULL = the object's stream).  ORBFE_E_CAPACITY when nframes > max_batch. */
+int orbfe_clahe_apply_batch_device(orbfe_clahe* c, const uint8_t* d_src, uint8_t* d_dst, int nframes, void* stream);
+/* one host image in, one host image out (steps in bytes; dst may be src); synchronous */
+int orbfe_clahe_apply(orbfe_clahe* c, const uint8_t* src, size_t sstep, uint8_t* dst, size_t dstep);
+/* stage test hook: the [tiles_y][tiles_x][256] lookup tables of frame `frame` of the last batch, to the host */
+int orbfe_clahe_lut(orbfe_clahe* c, int frame, uint8_t* out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -62,6 +62,8 @@ def lib():
     L.orc_knn2_ratio.argtypes = [vp, C.c_int, vp, C.c_int, C.c_double, vp, vp, vp]
     L.orc_remap_linear_u8.argtypes = [vp, C.c_int, C.c_int, C.c_int, vp, vp, vp, C.c_int]
     L.orc_to_gray.argtypes = [vp, C.c_longlong, C.c_int, C.c_int, vp]
+    L.orc_clahe_u8.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_double, C.c_int, C.c_int, vp, C.c_int, vp]
+    L.orc_clahe_u8.restype = C.c_int
     _lib = L
     return L
 
@@ -214,6 +216,17 @@ def to_gray(img, rgb):
     dst = np.zeros(img.shape[:2], np.uint8)
     lib().orc_to_gray(_ptr(img), img.shape[0] * img.shape[1], img.shape[2], int(rgb), _ptr(dst))
     return dst
+
+
+def clahe(img, clip=3.0, tiles=(8, 8), return_lut=False):
+    """cv::createCLAHE(clip, cv::Size(tiles[0], tiles[1]))->apply(img); tiles = (across, down)."""
+    img = np.ascontiguousarray(img, np.uint8)
+    dst = np.zeros_like(img)
+    lut = np.zeros((tiles[1], tiles[0], 256), np.uint8)
+    rc = lib().orc_clahe_u8(_ptr(img), img.shape[1], img.shape[0], img.shape[1], float(clip), tiles[0], tiles[1], _ptr(dst), img.shape[1], _ptr(lut))
+    if rc:
+        raise ValueError("image too small for the tile grid")
+    return (dst, lut) if return_lut else dst
 
 
 def merge_top2_host(parts, th, ratio, strict_lt):

@@ -71,6 +71,11 @@ SIGNATURES = {
     "orbfe_rectify_batch_device": (i32, [vp, vp, vp, i32, vp]),
     "orbfe_rectify": (i32, [vp, vp, sz, vp, sz]),
     "orbfe_to_gray_device": (i32, [i32, vp, i32, i32, i32, i32, i32, vp, vp]),
+    "orbfe_clahe_create": (i32, [i32, i32, i32, C.c_double, i32, i32, i32, C.POINTER(vp)]),
+    "orbfe_clahe_destroy": (None, [vp]),
+    "orbfe_clahe_apply_batch_device": (i32, [vp, vp, vp, i32, vp]),
+    "orbfe_clahe_apply": (i32, [vp, vp, sz, vp, sz]),
+    "orbfe_clahe_lut": (i32, [vp, i32, vp]),
     "orbfe_knn2_ratio": (i32, [i32, vp, i32, vp, i32, f64, vp, vp, vp]),
 }
 

@@ -5,11 +5,18 @@
  *                    maps from cv::initUndistortRectifyMap(..., CV_32F, ...) at :150-151)
  *   k_to_gray        cv::cvtColor(im, gray, RGB2GRAY / BGR2GRAY / RGBA2GRAY / BGRA2GRAY) of Tracking::GrabImage*
  *                    (/root/reference/src/Tracking.cc:1303-1328)
+ *   k_clahe_lut, k_clahe_apply   cv::createCLAHE(3.0, cv::Size(8, 8))->apply(im, im) of the TUM-VI drivers
+ *                    (/root/reference/Examples/Stereo-Inertial/stereo_inertial_tum_vi.cc:128-138, Examples/Monocular/mono_tum_vi.cc)
  * Arithmetic (verified bit-exact against cv2 4.13.0, tests/golden/conditioning.npz):
  *   remap: sx = cvRound(mapx*32), ix = sx >> 5, fx = sx & 31 (same for y, ix/iy saturated to int16); weights
  *          (32-fx)(32-fy)*32, fx(32-fy)*32, (32-fx)fy*32, fx*fy*32 (sum 2^15); dst = (sum w*tap + 2^14) >> 15; taps outside
  *          the image read 0.
- *   gray:  (R*9798 + G*19235 + B*3735 + 2^14) >> 15. */
+ *   gray:  (R*9798 + G*19235 + B*3735 + 2^14) >> 15.
+ *   clahe: per tile a 256-bin histogram (the image extended right/bottom with REFLECT_101 when its size is not a multiple of
+ *          the grid), bins clipped to max(int(clip*area/256), 1), the excess spread as excess/256 to every bin plus one more
+ *          to bins 0, s, 2s, ... (s = max(256/(excess%256), 1)), lut[k] = sat(cvRound(float(cumsum[k]) * (255.f/area)));
+ *          then each pixel blends the four neighbouring tiles' luts in fp32 without FMA:
+ *          (l11*xa1 + l12*xa)*ya1 + (l21*xa1 + l22*xa)*ya, xa = x*(1.f/tw) - .5f - floor(.), rounded with cvRound. */
 #include <cuda_runtime.h>
 #include <math.h>
 #include <stdint.h>
@@ -67,7 +74,181 @@ __global__ void __launch_bounds__(256) k_to_gray(const uint8_t* __restrict__ src
     dst[i] = (uint8_t)((r * 9798 + c1 * 19235 + b * 3735 + 16384) >> 15);
 }
 
+struct orbfe_clahe {
+    int device, W, H, tilesX, tilesY, tw, th, clipLimit, maxBatch;
+    float lutScale, invTw, invTh;
+    uint8_t* dLut;   /* [maxBatch][tilesY][tilesX][256] */
+    uint8_t* dImg;   /* staging for the host entry point */
+    cudaStream_t stream;
+};
+
+/* one CTA = one tile of one frame: histogram (one private copy per warp), clip, redistribute, prefix sum, lut */
+__global__ void __launch_bounds__(256) k_clahe_lut(const uint8_t* __restrict__ src, uint8_t* __restrict__ lut, int W, int H, int tilesX, int tw, int th,
+                                                   int clipLimit, float lutScale) {
+    __shared__ int hist[8][256];
+    __shared__ int wsum[8];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tile = blockIdx.x, txi = tile % tilesX, tyi = tile / tilesX;
+    const uint8_t* s = src + (size_t)blockIdx.y * W * H;
+#pragma unroll
+    for (int k = 0; k < 8; k++) hist[k][tid] = 0;
+    __syncthreads();
+    for (int r = warp; r < th; r += 8) {
+        const int y = tyi * th + r, sy = y < H ? y : 2 * H - 2 - y;
+        const uint8_t* row = s + (size_t)sy * W;
+        for (int c = lane; c < tw; c += 32) {
+            const int x = txi * tw + c;
+            atomicAdd(&hist[warp][row[x < W ? x : 2 * W - 2 - x]], 1);
+        }
+    }
+    __syncthreads();
+    int h = 0;
+#pragma unroll
+    for (int k = 0; k < 8; k++) h += hist[k][tid];
+    if (clipLimit > 0) {
+        int excess = max(h - clipLimit, 0);
+        h = min(h, clipLimit);
+#pragma unroll
+        for (int o = 16; o; o >>= 1) excess += __shfl_xor_sync(0xffffffffu, excess, o);
+        if (lane == 0) wsum[warp] = excess;
+        __syncthreads();
+        int clipped = 0;
+#pragma unroll
+        for (int k = 0; k < 8; k++) clipped += wsum[k];
+        const int redist = clipped >> 8, residual = clipped & 255;
+        h += redist;
+        if (residual) {
+            const int step = max(256 / residual, 1);
+            if (tid % step == 0 && tid / step < residual) h++;
+        }
+        __syncthreads();
+    }
+    int sum = h; /* inclusive prefix sum over the 256 bins */
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, sum, o);
+        if (lane >= o) sum += t;
+    }
+    if (lane == 31) wsum[warp] = sum;
+    __syncthreads();
+    for (int k = 0; k < warp; k++) sum += wsum[k];
+    const int v = __float2int_rn(__fmul_rn((float)sum, lutScale));
+    lut[((size_t)blockIdx.y * gridDim.x + tile) * 256 + tid] = (uint8_t)min(max(v, 0), 255);
+}
+
+/* one thread = four adjacent pixels of one row; src == dst is allowed (each pixel depends on itself and the luts only) */
+__global__ void __launch_bounds__(256) k_clahe_apply(const uint8_t* __restrict__ src, const uint8_t* __restrict__ lut, uint8_t* __restrict__ dst, int W, int H,
+                                                     int tilesX, int tilesY, float invTw, float invTh, int groupsPerRow) {
+    const int g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= groupsPerRow * H) return;
+    const int y = g / groupsPerRow, x0 = (g - y * groupsPerRow) * 4;
+    const size_t frame = (size_t)blockIdx.y * W * H;
+    const uint8_t* l = lut + (size_t)blockIdx.y * tilesX * tilesY * 256;
+    const float tyf = __fsub_rn(__fmul_rn((float)y, invTh), 0.5f);
+    int ty1 = __float2int_rd(tyf);
+    const float ya = __fsub_rn(tyf, (float)ty1), ya1 = __fsub_rn(1.0f, ya);
+    const int ty2 = min(ty1 + 1, tilesY - 1);
+    ty1 = max(ty1, 0);
+    const uint8_t* l1 = l + (size_t)ty1 * tilesX * 256;
+    const uint8_t* l2 = l + (size_t)ty2 * tilesX * 256;
+    const uint8_t* sp = src + frame + (size_t)y * W + x0;
+    uint8_t* dp = dst + frame + (size_t)y * W + x0;
+    const bool word = x0 + 4 <= W && ((reinterpret_cast<uintptr_t>(sp) | reinterpret_cast<uintptr_t>(dp)) & 3) == 0;
+    uint32_t in = 0, out = 0;
+    if (word) in = *reinterpret_cast<const uint32_t*>(sp);
+    else
+        for (int k = 0; k < 4 && x0 + k < W; k++) in |= (uint32_t)sp[k] << (8 * k);
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const int x = x0 + k;
+        if (x >= W) break;
+        const float txf = __fsub_rn(__fmul_rn((float)x, invTw), 0.5f);
+        int tx1 = __float2int_rd(txf);
+        const float xa = __fsub_rn(txf, (float)tx1), xa1 = __fsub_rn(1.0f, xa);
+        const int tx2 = min(tx1 + 1, tilesX - 1);
+        tx1 = max(tx1, 0);
+        const int v = (in >> (8 * k)) & 255;
+        const float a = (float)l1[tx1 * 256 + v], b = (float)l1[tx2 * 256 + v], c = (float)l2[tx1 * 256 + v], d = (float)l2[tx2 * 256 + v];
+        const float top = __fadd_rn(__fmul_rn(a, xa1), __fmul_rn(b, xa)), bot = __fadd_rn(__fmul_rn(c, xa1), __fmul_rn(d, xa));
+        const int r = __float2int_rn(__fadd_rn(__fmul_rn(top, ya1), __fmul_rn(bot, ya)));
+        out |= (uint32_t)min(max(r, 0), 255) << (8 * k);
+    }
+    if (word) *reinterpret_cast<uint32_t*>(dp) = out;
+    else
+        for (int k = 0; k < 4 && x0 + k < W; k++) dp[k] = (uint8_t)(out >> (8 * k));
+}
+
 extern "C" {
+
+void orbfe_clahe_destroy(orbfe_clahe* c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    cudaFree(c->dLut); cudaFree(c->dImg);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+int orbfe_clahe_create(int device, int width, int height, double clip_limit, int tiles_x, int tiles_y, int max_batch, orbfe_clahe** out) {
+    if (!out || width < 1 || height < 1 || width > 16384 || height > 16384 || tiles_x < 1 || tiles_y < 1 || tiles_x > 64 || tiles_y > 64 ||
+        max_batch < 1 || max_batch > 65535) { orbfe_set_error("bad argument"); return ORBFE_E_INVALID; }
+    *out = nullptr;
+    const bool whole = width % tiles_x == 0 && height % tiles_y == 0;
+    const int ew = whole ? width : width + tiles_x - width % tiles_x, eh = whole ? height : height + tiles_y - height % tiles_y;
+    if (ew - width >= width || eh - height >= height) { orbfe_set_error("image %dx%d too small for a %dx%d tile grid", width, height, tiles_x, tiles_y); return ORBFE_E_INVALID; }
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev) {
+        orbfe_set_error("no usable CUDA device %d (found %d); this library has no CPU path", device, ndev);
+        return ORBFE_E_CUDA;
+    }
+    ORBFE_CUDA(cudaSetDevice(device));
+    orbfe_clahe* c = new (std::nothrow) orbfe_clahe();
+    if (!c) return ORBFE_E_INVALID;
+    c->device = device; c->W = width; c->H = height; c->tilesX = tiles_x; c->tilesY = tiles_y; c->maxBatch = max_batch;
+    c->tw = ew / tiles_x; c->th = eh / tiles_y;
+    const int area = c->tw * c->th;
+    c->clipLimit = 0;
+    if (clip_limit > 0.0) { c->clipLimit = (int)(clip_limit * area / 256); if (c->clipLimit < 1) c->clipLimit = 1; }
+    c->lutScale = 255.0f / (float)area; c->invTw = 1.0f / (float)c->tw; c->invTh = 1.0f / (float)c->th;
+    c->dLut = nullptr; c->dImg = nullptr; c->stream = nullptr;
+    cudaError_t e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaMalloc((void**)&c->dLut, (size_t)max_batch * tiles_x * tiles_y * 256);
+    if (e == cudaSuccess) e = cudaMalloc((void**)&c->dImg, (size_t)width * height);
+    if (e != cudaSuccess) { const int rc = orbfe_cuda_fail(e, "clahe allocation"); orbfe_clahe_destroy(c); return rc; }
+    *out = c;
+    return ORBFE_OK;
+}
+
+int orbfe_clahe_apply_batch_device(orbfe_clahe* c, const uint8_t* d_src, uint8_t* d_dst, int nframes, void* stream) {
+    if (!c || !d_src || !d_dst || nframes < 1) { orbfe_set_error("bad argument"); return ORBFE_E_INVALID; }
+    if (nframes > c->maxBatch) { orbfe_set_error("batch of %d frames exceeds max_batch %d", nframes, c->maxBatch); return ORBFE_E_CAPACITY; }
+    ORBFE_CUDA(cudaSetDevice(c->device));
+    cudaStream_t st = stream ? (cudaStream_t)stream : c->stream;
+    k_clahe_lut<<<dim3(c->tilesX * c->tilesY, nframes), 256, 0, st>>>(d_src, c->dLut, c->W, c->H, c->tilesX, c->tw, c->th, c->clipLimit, c->lutScale);
+    const int gpr = (c->W + 3) / 4;
+    k_clahe_apply<<<dim3((gpr * c->H + 255) / 256, nframes), 256, 0, st>>>(d_src, c->dLut, d_dst, c->W, c->H, c->tilesX, c->tilesY, c->invTw, c->invTh, gpr);
+    ORBFE_CUDA(cudaGetLastError());
+    return ORBFE_OK;
+}
+
+int orbfe_clahe_apply(orbfe_clahe* c, const uint8_t* src, size_t sstep, uint8_t* dst, size_t dstep) {
+    if (!c || !src || !dst || sstep < (size_t)c->W || dstep < (size_t)c->W) { orbfe_set_error("bad argument"); return ORBFE_E_INVALID; }
+    ORBFE_CUDA(cudaSetDevice(c->device));
+    ORBFE_CUDA(cudaMemcpy2DAsync(c->dImg, c->W, src, sstep, c->W, c->H, cudaMemcpyHostToDevice, c->stream));
+    int rc = orbfe_clahe_apply_batch_device(c, c->dImg, c->dImg, 1, c->stream);
+    if (rc) return rc;
+    ORBFE_CUDA(cudaMemcpy2DAsync(dst, dstep, c->dImg, c->W, c->W, c->H, cudaMemcpyDeviceToHost, c->stream));
+    ORBFE_CUDA(cudaStreamSynchronize(c->stream));
+    return ORBFE_OK;
+}
+
+int orbfe_clahe_lut(orbfe_clahe* c, int frame, uint8_t* out) {
+    if (!c || !out || frame < 0 || frame >= c->maxBatch) { orbfe_set_error("bad argument"); return ORBFE_E_INVALID; }
+    ORBFE_CUDA(cudaSetDevice(c->device));
+    ORBFE_CUDA(cudaDeviceSynchronize());
+    ORBFE_CUDA(cudaMemcpy(out, c->dLut + (size_t)frame * c->tilesX * c->tilesY * 256, (size_t)c->tilesX * c->tilesY * 256, cudaMemcpyDeviceToHost));
+    return ORBFE_OK;
+}
 
 void orbfe_rectifier_destroy(orbfe_rectifier* r) {
     if (!r) return;

@@ -1,4 +1,4 @@
-"""Input conditioning: cv::remap rectification and colour-to-gray.  CPU: the oracle against cv2's own
+"""Input conditioning: cv::remap rectification, colour-to-gray and CLAHE.  CPU: the oracle against cv2's own
 outputs (tests/golden/conditioning.npz); GPU: the kernels against the oracle and the goldens, bit-exact."""
 import os
 
@@ -19,6 +19,38 @@ def test_oracle_remap_and_gray_match_cv2():
     assert np.array_equal(O.to_gray(np.ascontiguousarray(col[..., :3]), False), g["gray_bgr"])
     assert np.array_equal(O.to_gray(col, True), g["gray_rgba"])
     assert np.array_equal(O.to_gray(col, False), g["gray_bgra"])
+
+
+def _sha(a):
+    import hashlib
+    return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+
+
+def _clahe_cases(g):
+    """(name, source image, clip, tiles(across, down), cv2 output or its sha)"""
+    from orb_slam3_detailed_comments_kor_b200 import synth
+    L, _ = synth.stereo_pair(1, 512, 512)
+    dark = (L // 3 + 20).astype(np.uint8)
+    assert _sha(dark) == str(g["clahe_tumvi_src_sha"][0]), "synthetic generator drifted"
+    E, _ = synth.stereo_pair(0, 752, 480)
+    cases = [("tumvi", dark, 3.0, (8, 8), str(g["clahe_tumvi_sha"][0])), ("euroc", E, 3.0, (8, 8), str(g["clahe_euroc_sha"][0]))]
+    for tag in "abc":
+        cases.append((tag, g["clahe_src_" + tag], 3.0, (8, 8), g["clahe_out_" + tag]))
+    cases.append(("flat", np.full((64, 64), 77, np.uint8), 3.0, (8, 8), g["clahe_flat_out"]))
+    cases.append(("d", g["clahe_src_a"], 40.0, (4, 6), g["clahe_out_d"]))
+    return cases
+
+
+def _same(out, want):
+    return _sha(out) == want if isinstance(want, str) else np.array_equal(out, want)
+
+
+def test_oracle_clahe_matches_cv2():
+    g = np.load(GOLD)
+    for name, src, clip, tiles, want in _clahe_cases(g):
+        assert _same(O.clahe(src, clip, tiles), want), name
+    with pytest.raises(ValueError):
+        O.clahe(np.zeros((3, 100), np.uint8))           # 3 rows cannot be reflected out to 8 tile rows
 
 
 @pytest.mark.gpu
@@ -71,3 +103,40 @@ def test_gpu_gray_matches_oracle_and_cv2():
         out = d_dst.cpu().numpy()
         assert np.array_equal(out[0], g[key]), key
         assert np.array_equal(out[1], O.to_gray(batch[1], rgb)), key
+
+
+@pytest.mark.gpu
+def test_gpu_clahe_matches_oracle_and_cv2():
+    import torch
+    from orb_slam3_detailed_comments_kor_b200 import synth
+    from orb_slam3_detailed_comments_kor_b200._lib import OrbfeError
+    from orb_slam3_detailed_comments_kor_b200.conditioning import CLAHE
+    g = np.load(GOLD)
+    for name, src, clip, tiles, want in _clahe_cases(g):
+        c = CLAHE(src.shape[1], src.shape[0], clip, tiles)
+        out = c.apply(src)
+        ref, lut = O.clahe(src, clip, tiles, return_lut=True)
+        assert np.array_equal(c.lut(0), lut), name + ": lookup tables"
+        assert np.array_equal(out, ref) and _same(out, want), name
+        c.close()
+    # a TUM-VI sized batch, device to device, in place, frames at different brightness
+    W = H = 512
+    frames = []
+    for f in range(5):
+        L, R = synth.stereo_pair(40 + f, W, H)
+        frames += [(L // (f + 1)).astype(np.uint8), R]
+    batch = np.stack(frames)
+    c = CLAHE(W, H, 3.0, (8, 8), max_batch=len(frames))
+    st = torch.cuda.Stream()
+    with torch.cuda.stream(st):
+        d = torch.from_numpy(batch).cuda()
+        c.batch_device(d.data_ptr(), d.data_ptr(), len(frames), stream=st.cuda_stream)
+        out = d.cpu().numpy()
+    st.synchronize()
+    for f in range(len(frames)):
+        assert np.array_equal(out[f], O.clahe(batch[f])), "frame %d" % f
+    with pytest.raises(OrbfeError):
+        c.batch_device(d.data_ptr(), d.data_ptr(), len(frames) + 1, stream=st.cuda_stream)
+    c.close()
+    with pytest.raises(OrbfeError):
+        CLAHE(100, 3)

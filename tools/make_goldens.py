@@ -465,6 +465,24 @@ def main():
     cond["gray_bgr"] = cv2.cvtColor(np.ascontiguousarray(col[..., :3]), cv2.COLOR_BGR2GRAY)
     cond["gray_rgba"] = cv2.cvtColor(col, cv2.COLOR_RGBA2GRAY)
     cond["gray_bgra"] = cv2.cvtColor(col, cv2.COLOR_BGRA2GRAY)
+    # CLAHE exactly as the TUM-VI drivers build it: cv::createCLAHE(3.0, cv::Size(8, 8))
+    clahe = cv2.createCLAHE(clipLimit=3.0, tileGridSize=(8, 8))
+    L, _ = synth.stereo_pair(1, 512, 512)                 # the tumvi case's left image (dark-ish version: CLAHE has work to do)
+    dark = (L // 3 + 20).astype(np.uint8)
+    cond["clahe_tumvi_src_sha"] = np.array([sha(dark)])
+    cond["clahe_tumvi_sha"] = np.array([sha(clahe.apply(dark))])
+    E, _ = synth.stereo_pair(0, 752, 480)
+    cond["clahe_euroc_sha"] = np.array([sha(clahe.apply(E))])
+    for tag, (h, w) in (("a", (70, 100)), ("b", (64, 100)), ("c", (61, 88))):    # sizes that do not divide by 8 (one or both ways)
+        im = np.clip(rng.normal(120, 30, (h, w)), 0, 255).astype(np.uint8)
+        im[5:25, 10:50] = np.clip(im[5:25, 10:50].astype(np.int32) + 90, 0, 255)
+        im[40:, 60:] //= 4
+        cond["clahe_src_" + tag] = im
+        cond["clahe_out_" + tag] = clahe.apply(im)
+    flat = np.full((64, 64), 77, np.uint8)                # a constant image: every histogram is one clipped bin
+    cond["clahe_flat_out"] = clahe.apply(flat)
+    c2 = cv2.createCLAHE(clipLimit=40.0, tileGridSize=(4, 6))
+    cond["clahe_out_d"] = c2.apply(cond["clahe_src_a"])   # other parameters: clip 40, 4 x 6 tiles (cv::Size(4, 6): 4 across)
     np.savez_compressed(os.path.join(out_dir, "conditioning.npz"), **cond)
     print("wrote goldens to", out_dir, "cv2", cv2.__version__)
 
