@@ -412,6 +412,41 @@ def main():
                             "peak_source": "148 SM x 16 POPC/clk x sm_max_mhz / 8 POPC per pair (nominal; SURVEY.md §8d)",
                             "note": "accounting stays at 8 algorithmic POPC per pair; the kernel issues 6 (two carry-save adders), so > 1.0 is possible"}}
 
+    # ---- projection-gated search: Tracking::SearchLocalPoints-sized frames, one CTA per frame
+    from orb_slam3_detailed_comments_kor_b200 import projection as PJ
+    from orb_slam3_detailed_comments_kor_b200.synth import projection_cases as PC
+    pj_cases = [PC.make_case(seed=900 + i, n=1200, nq=1500, W=W, H=H, th=1.0, stereo_gate=True) for i in range(8)]
+    PF = 512                                                              # frames per step per GPU (the 8 distinct ones, tiled)
+    pj_order = [pj_cases[i % 8] for i in range(PF)]
+    pj_cat = lambda k: np.concatenate([c[k] for c in pj_order])  # noqa: E731
+    pj_koff = np.cumsum([0] + [len(c["kps"]) for c in pj_order]).astype(np.int32)
+    pj_qoff = np.cumsum([0] + [len(c["queries"]) for c in pj_order]).astype(np.int32)
+    to_dev = lambda a: torch.from_numpy(np.ascontiguousarray(a).view(np.uint8).reshape(-1)).cuda()  # noqa: E731
+    pj_d = {k: to_dev(pj_cat(k)) for k in ("kps", "desc", "queries", "qdesc", "u_right", "taken")}
+    pj_d["grid"] = to_dev(np.stack([c["grid"] for c in pj_order]))
+    pj_d["koff"], pj_d["qoff"] = to_dev(pj_koff), to_dev(pj_qoff)
+    pj_out = torch.zeros(int(pj_qoff[-1]) * 28, dtype=torch.uint8, device="cuda")
+    torch.cuda.synchronize()
+
+    def pj_step():
+        PJ.search_by_projection_device(PF, 4096, pj_d["kps"].data_ptr(), pj_d["desc"].data_ptr(), pj_d["koff"].data_ptr(), pj_d["grid"].data_ptr(),
+                                       pj_d["queries"].data_ptr(), pj_d["qdesc"].data_ptr(), pj_d["qoff"].data_ptr(), pj_out.data_ptr(),
+                                       d_u_right=pj_d["u_right"].data_ptr(), d_taken_in=pj_d["taken"].data_ptr(), device=local_rank, stream=st)
+
+    for _ in range(3):
+        pj_step()
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        pj_step()
+    e1.record()
+    barrier()
+    pj_ms = max_over_ranks(e0.elapsed_time(e1) / args.steps)
+    pj_acc = int(pj_out.cpu().numpy().view(PJ.PROJ_MATCH_DTYPE)["accepted"].sum())
+    projection = {"value": int(pj_qoff[-1]) * world / (pj_ms / 1e3), "unit": "map_point_searches/s", "frames_per_s": PF * world / (pj_ms / 1e3),
+                  "ms_per_step": pj_ms, "frames_per_step": PF * world, "keypoints_per_frame": 1200, "map_points_per_frame": int(pj_qoff[1]),
+                  "accepted_per_step": pj_acc, "note": "ORBmatcher::SearchByProjection(Frame&, vpMapPoints, th=1) incl. the frame grid; device resident"}
+
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cores = os.cpu_count() or 1
@@ -421,6 +456,19 @@ def main():
         cpu = {"value": rate, "unit": "frames/s", "cores": cores, "kind": "port",
                "sample": "%d stereo pairs (%.1f s wall) frame-parallel over %d threads; oracle built -O3 -march=x86-64-v3" % (sample, dt, cores),
                "hamming": {"value": hrate, "unit": "descriptor_pairs/s", "sample": "%d queries x %d rows (%.1f s wall)" % (nq, ndb, hdt)}}
+        from oracle import orb_oracle as O
+        reps = 64 * cores
+
+        def pj_cpu(i):
+            c = pj_cases[i % 8]
+            O.search_by_projection(c["kps"], c["desc"], c["queries"], c["qdesc"], c["grid"], u_right=c["u_right"], taken=c["taken"])
+
+        t0 = time.perf_counter()
+        with ThreadPoolExecutor(cores) as tp:
+            list(tp.map(pj_cpu, range(reps)))
+        pdt = time.perf_counter() - t0
+        cpu["projection"] = {"value": reps * int(pj_qoff[1]) / pdt, "unit": "map_point_searches/s",
+                             "sample": "%d frames (%.2f s wall) frame-parallel over %d threads" % (reps, pdt, cores)}
 
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
@@ -430,7 +478,7 @@ def main():
                            "l2": "inputs_larger_than_L2 (%d MB of images per step per GPU)" % (2 * P * W * H >> 20),
                            "mean_keypoints_per_frame": nkp, "parallelism": "frames sharded by rank, no collective"},
                 "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
-                "single_frame_latency_ms": single_ms, "rectify": rectify,
+                "single_frame_latency_ms": single_ms, "rectify": rectify, "projection": projection,
                 "gpu_launches": (2 * (PARAMS[2] + 8) + 3) * args.steps,
                 "hamming": hamming}
         print(json.dumps(line), flush=True)

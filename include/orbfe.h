@@ -183,6 +183,65 @@ int orbfe_hamming_top2(int device, const uint8_t* q, int nq, const uint8_t* db, 
 int orbfe_knn2_ratio(int device, const uint8_t* q, int nq, const uint8_t* t, int nt, double ratio, int32_t* match,
                      int32_t* d0, int32_t* d1);
 
+/* ------------------------------------------------------------------------------- projection-gated search (N1) */
+/* Replaces the search of Tracking::SearchLocalPoints (src/Tracking.cc:3430-3524):
+ *   int ORBmatcher::SearchByProjection(Frame &F, const vector<MapPoint*> &vpMapPoints, const float th, const bool bFarPoints,
+ *                                      const float thFarPoints)                                   (src/ORBmatcher.cc:44-214)
+ * including the frame grid it walks: Frame::AssignFeaturesToGrid / PosInGrid (src/Frame.cc:380-411, 711-721; 64 x 48 cells,
+ * include/Frame.h:37-38) and Frame::GetFeaturesInArea (src/Frame.cc:643-709).  The result is the reference's, including its
+ * serial rule that a matched map point occupies its keypoint for the map points after it. */
+typedef struct orbfe_frame_grid {   /* Frame::mnMinX, mnMinY, mfGridElementWidthInv, mfGridElementHeightInv */
+    float min_x, min_y, inv_w, inv_h;
+} orbfe_frame_grid;
+
+#define ORBFE_PQ_RIGHT 1       /* search the right camera's keypoints (bRight; rows >= n_left) */
+#define ORBFE_PQ_BLOCKS 2      /* pMP->Observations() > 0: once matched, later map points skip the keypoint (:91-93) */
+#define ORBFE_PQ_SKIP 4        /* not in view / bad / too far (:52-59): no search */
+#define ORBFE_PQ_AFTER_LEFT 8  /* right-camera half (:145-211) of the map point of the query before: not run when that one
+                                  failed the ratio test (the `continue` at :117-118 leaves the whole iteration) */
+typedef struct orbfe_proj_query {   /* one (map point, camera) search, in the reference's loop order */
+    float x, y;        /* mTrackProjX, mTrackProjY (mTrackProjXR, mTrackProjYR with ORBFE_PQ_RIGHT) */
+    float radius;      /* RadiusByViewingCos(mTrackViewCos) [* th] * F.mvScaleFactors[nPredictedLevel] (:67-73) */
+    float xr;          /* mTrackProjXR, for the |xr - mvuRight| gate (:95-100); read only when u_right is given */
+    int32_t min_level; /* nPredictedLevel - 1 */
+    int32_t max_level; /* nPredictedLevel */
+    int32_t flags;     /* ORBFE_PQ_* */
+} orbfe_proj_query;
+
+#define ORBFE_PS_NO_CANDIDATES 0   /* empty window, or every candidate occupied / gated out */
+#define ORBFE_PS_ACCEPTED 1
+#define ORBFE_PS_OVER_THRESHOLD 2  /* bestDist > TH_HIGH */
+#define ORBFE_PS_RATIO_REJECTED 3  /* bestLevel == bestLevel2 && bestDist > mfNNratio * bestDist2 */
+#define ORBFE_PS_SKIPPED 4         /* ORBFE_PQ_SKIP */
+#define ORBFE_PS_CAPACITY 5        /* the frame holds more keypoints than promised: nothing was searched */
+#define ORBFE_PS_DROPPED 6         /* ORBFE_PQ_AFTER_LEFT and the left half was ratio-rejected */
+typedef struct orbfe_proj_match {
+    int32_t best_idx;      /* bestIdx as a row of the frame's keypoint array (right camera: local index + n_left); -1 if none */
+    int32_t best_dist, best_level, second_dist, second_level;   /* bestDist, bestLevel, bestDist2, bestLevel2 (256 / -1 when unset) */
+    int32_t accepted;      /* 1: F.mvpMapPoints[best_idx] = pMP (and its stereo partner row, if any) */
+    int32_t status;        /* ORBFE_PS_* */
+} orbfe_proj_match;
+
+/* A batch of frames, everything on the device, asynchronous on `stream`, no allocation.
+ *   d_kps / d_desc: the frames' keypoints (pt and octave are read: mvKeysUn for a rectified rig, mvKeys followed by mvKeysRight
+ *     for a fisheye rig) and 32-byte descriptors, frame f = rows [d_kp_offsets[f], d_kp_offsets[f+1]); at most max_keypoints
+ *     (<= 4096) rows per frame, a frame with more gets ORBFE_PS_CAPACITY in every result;
+ *   d_n_left: per frame F.Nleft (-1: one grid), or NULL for all -1;   d_u_right: mvuRight per row, or NULL;
+ *   d_partner: per row the row matched in the other camera (mvLeftToRightMatch[i] + Nleft / mvRightToLeftMatch[i - Nleft]) or
+ *     -1, or NULL;   d_taken_in: per row, nonzero iff F.mvpMapPoints[row] has observations (NULL: none);
+ *   d_queries / d_qdesc (pMP->GetDescriptor()): frame f = entries [d_q_offsets[f], d_q_offsets[f+1]);
+ *   th_high = ORBmatcher::TH_HIGH (100), nnratio = mfNNratio;   d_taken_out (may be NULL or d_taken_in): occupancy afterwards. */
+int orbfe_search_by_projection_device(int device, int nframes, int max_keypoints, const orbfe_keypoint* d_kps, const uint8_t* d_desc,
+                                      const int32_t* d_kp_offsets, const int32_t* d_n_left, const float* d_u_right, const int32_t* d_partner,
+                                      const uint8_t* d_taken_in, const orbfe_frame_grid* d_grids, const orbfe_proj_query* d_queries,
+                                      const uint8_t* d_qdesc, const int32_t* d_q_offsets, int th_high, float nnratio, orbfe_proj_match* d_out,
+                                      uint8_t* d_taken_out, void* stream);
+/* One frame over host memory (copies inside, synchronous).  taken is updated in place (may be NULL); *nmatches receives the
+ * reference's return value (an accepted row with a stereo partner counts twice). */
+int orbfe_search_by_projection(int device, const orbfe_keypoint* kps, const uint8_t* desc, int n, int n_left, const float* u_right,
+                               const int32_t* partner, uint8_t* taken, const orbfe_frame_grid* grid, const orbfe_proj_query* queries,
+                               const uint8_t* qdesc, int nq, int th_high, float nnratio, orbfe_proj_match* out, int* nmatches);
+
 /* ------------------------------------------------------------------------------------------ input conditioning */
 /* The steps the example drivers and Tracking run on each image before the extractor, so that an
  * uploaded frame can stay on the GPU.  Bit-exact with OpenCV 4.13's 8-bit fixed-point paths. */

@@ -3,8 +3,9 @@
  *
  * Only the hot-path members are provided: the constants, the constructor, the static DescriptorDistance, the
  * brute-force top-2 core that SearchByBoW's inner loops perform (src/ORBmatcher.cc:311-375, 870-908), and free
- * functions carrying the bodies of Frame::ComputeStereoMatches / ComputeStereoFishEyeMatches's matching step.
- * The projection / BoW-node gating around that core stays in the reference's ORBmatcher.cc. */
+ * functions carrying the bodies of Frame::ComputeStereoMatches / ComputeStereoFishEyeMatches's matching step and of
+ * SearchByProjection(Frame&, vpMapPoints, th, ...) (src/ORBmatcher.cc:44-214).
+ * The BoW-node gating and the other projection overloads stay in the reference's ORBmatcher.cc. */
 #ifndef ORBFE_SHIM_ORBMATCHER_H
 #define ORBFE_SHIM_ORBMATCHER_H
 
@@ -79,6 +80,35 @@ inline void FishEyeKnnMatches(const cv::Mat& stereoDescLeft, const cv::Mat& ster
     for (int i = 0; i < stereoDescRight.rows; i++) std::memcpy(&t[(size_t)i * 32], stereoDescRight.ptr<unsigned char>(i), 32);
     if (orbfe_knn2_ratio(device, q.data(), stereoDescLeft.rows, t.data(), stereoDescRight.rows, 0.7, match.data(), nullptr, nullptr) != ORBFE_OK)
         throw std::runtime_error(std::string("orbfe_knn2_ratio: ") + orbfe_last_error());
+}
+
+/* The loop of ORBmatcher::SearchByProjection(Frame &F, const vector<MapPoint*> &vpMapPoints, th, bFarPoints, thFarPoints)
+ * (src/ORBmatcher.cc:44-214) on the frame's arrays; the grid of Frame::AssignFeaturesToGrid is rebuilt on the GPU.
+ *   keys / descriptors: F.mvKeysUn + F.mDescriptors (Nleft == -1) or mvKeys followed by mvKeysRight (fisheye rig);
+ *   uRight: &F.mvuRight or NULL;   partner: per row the row matched in the other camera or -1 (see orbfe.h), or NULL;
+ *   taken[row] != 0 iff F.mvpMapPoints[row] has observations — updated in place;
+ *   queries[k] / queryDescriptors.row(k): one entry per (map point, camera) search the reference loop would start, in its order
+ *   (fields in orbfe.h cite the members they come from).
+ * The caller then assigns F.mvpMapPoints[out[k].best_idx] = pMP (and the partner row) for every out[k].accepted, in order.
+ * Returns nmatches as the reference counts them. */
+inline int SearchByProjection(const std::vector<cv::KeyPoint>& keys, const cv::Mat& descriptors, int Nleft, const std::vector<float>* uRight,
+                              const std::vector<int>* partner, std::vector<unsigned char>& taken, float mnMinX, float mnMinY,
+                              float mfGridElementWidthInv, float mfGridElementHeightInv, const std::vector<orbfe_proj_query>& queries,
+                              const cv::Mat& queryDescriptors, float mfNNratio, std::vector<orbfe_proj_match>& out, int device = 0) {
+    static_assert(sizeof(cv::KeyPoint) == sizeof(orbfe_keypoint), "cv::KeyPoint layout");
+    const int n = (int)keys.size(), nq = (int)queries.size();
+    out.resize(nq);
+    taken.resize(n, 0);
+    std::vector<unsigned char> d((size_t)n * 32), qd((size_t)nq * 32);
+    for (int i = 0; i < n; i++) std::memcpy(&d[(size_t)i * 32], descriptors.ptr<unsigned char>(i), 32);
+    for (int i = 0; i < nq; i++) std::memcpy(&qd[(size_t)i * 32], queryDescriptors.ptr<unsigned char>(i), 32);
+    const orbfe_frame_grid grid = {mnMinX, mnMinY, mfGridElementWidthInv, mfGridElementHeightInv};
+    int nmatches = 0;
+    if (orbfe_search_by_projection(device, reinterpret_cast<const orbfe_keypoint*>(keys.data()), d.data(), n, Nleft, uRight ? uRight->data() : nullptr,
+                                   partner ? partner->data() : nullptr, taken.data(), &grid, queries.data(), qd.data(), nq, ORBmatcher::TH_HIGH,
+                                   mfNNratio, out.data(), &nmatches) != ORBFE_OK)
+        throw std::runtime_error(std::string("orbfe_search_by_projection: ") + orbfe_last_error());
+    return nmatches;
 }
 
 }  // namespace ORB_SLAM3

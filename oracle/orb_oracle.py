@@ -62,6 +62,8 @@ def lib():
     L.orc_knn2_ratio.argtypes = [vp, C.c_int, vp, C.c_int, C.c_double, vp, vp, vp]
     L.orc_remap_linear_u8.argtypes = [vp, C.c_int, C.c_int, C.c_int, vp, vp, vp, C.c_int]
     L.orc_to_gray.argtypes = [vp, C.c_longlong, C.c_int, C.c_int, vp]
+    L.orc_search_by_projection.argtypes = [vp, vp, C.c_int, C.c_int, vp, vp, vp, vp, vp, vp, C.c_int, C.c_int, C.c_float, vp]
+    L.orc_search_by_projection.restype = C.c_int
     L.orc_clahe_u8.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_double, C.c_int, C.c_int, vp, C.c_int, vp]
     L.orc_clahe_u8.restype = C.c_int
     _lib = L
@@ -216,6 +218,29 @@ def to_gray(img, rgb):
     dst = np.zeros(img.shape[:2], np.uint8)
     lib().orc_to_gray(_ptr(img), img.shape[0] * img.shape[1], img.shape[2], int(rgb), _ptr(dst))
     return dst
+
+
+PROJ_QUERY_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("radius", "<f4"), ("xr", "<f4"), ("min_level", "<i4"), ("max_level", "<i4"),
+                             ("flags", "<i4")])
+PROJ_MATCH_DTYPE = np.dtype([("best_idx", "<i4"), ("best_dist", "<i4"), ("best_level", "<i4"), ("second_dist", "<i4"),
+                             ("second_level", "<i4"), ("accepted", "<i4"), ("status", "<i4")])
+
+
+def search_by_projection(kps, desc, queries, qdesc, grid, n_left=-1, u_right=None, partner=None, taken=None, th_high=100, nnratio=0.8):
+    """ORBmatcher::SearchByProjection(Frame&, vpMapPoints, th) on arrays, serial.  Returns (matches, taken_after, nmatches)."""
+    kps = np.ascontiguousarray(kps, KP_DTYPE)
+    desc = np.ascontiguousarray(desc, np.uint8)
+    queries = np.ascontiguousarray(queries, PROJ_QUERY_DTYPE)
+    qdesc = np.ascontiguousarray(qdesc, np.uint8)
+    grid = np.ascontiguousarray(grid, np.float32)
+    ur = None if u_right is None else np.ascontiguousarray(u_right, np.float32)
+    pt = None if partner is None else np.ascontiguousarray(partner, np.int32)
+    tk = np.zeros(kps.shape[0], np.uint8) if taken is None else np.array(taken, np.uint8)
+    out = np.zeros(queries.shape[0], PROJ_MATCH_DTYPE)
+    nm = lib().orc_search_by_projection(_ptr(kps), _ptr(desc), kps.shape[0], n_left, _ptr(ur) if ur is not None else None,
+                                        _ptr(pt) if pt is not None else None, _ptr(tk), _ptr(grid), _ptr(queries), _ptr(qdesc),
+                                        queries.shape[0], th_high, nnratio, _ptr(out))
+    return out, tk, nm
 
 
 def clahe(img, clip=3.0, tiles=(8, 8), return_lut=False):

@@ -1,0 +1,345 @@
+/* orbfe_project.cu — projection-gated descriptor search: the search of Tracking::SearchLocalPoints,
+ *   ORBmatcher::SearchByProjection(Frame&, const vector<MapPoint*>&, th, bFarPoints, thFarPoints)   /root/reference/src/ORBmatcher.cc:44-214
+ * together with the frame grid it walks,
+ *   Frame::AssignFeaturesToGrid / PosInGrid   /root/reference/src/Frame.cc:380-411, 711-721   (64 x 48 cells, include/Frame.h:37-38)
+ *   Frame::GetFeaturesInArea                  /root/reference/src/Frame.cc:643-709
+ *
+ * One CTA = one frame; frames of a batch are independent.  The grid (both cameras' halves for a fisheye rig) is built in
+ * shared memory as a counting sort whose cell lists are ascending keypoint rows, i.e. the reference's push_back order.
+ *
+ * The reference loop is serial: a map point that gets matched occupies its keypoint, and the map points after it skip that
+ * keypoint.  The kernel reproduces that result exactly with rounds of speculation.  In every round each unresolved query
+ *   A. stamps its index (atomicMin) on every keypoint it could still take: the candidates of its window and their stereo
+ *      partners;
+ *   B. scans its window against the keypoints taken so far, with the reference's best/second update rule, and becomes final
+ *      iff no keypoint that can change its outcome — a candidate whose distance is <= its second-best distance, or the
+ *      partner of its best — carries the stamp of an earlier unresolved query (the outcome of the scan depends only on the
+ *      candidates at or below the second-best distance).  The keypoints it takes become visible in the next round.
+ * The earliest unresolved query always becomes final, so the loop ends; with the small windows of tracking (radius 2.5-4 px
+ * times the level scale) almost everything resolves in the first rounds. */
+#include <cuda_runtime.h>
+#include <limits.h>
+#include <stdint.h>
+
+#include "orbfe_internal.h"
+
+#define PJ_NT 256
+#define PJ_MAXKP 4096
+#define PJ_COLS 64
+#define PJ_ROWS 48
+#define PJ_CELLS (PJ_COLS * PJ_ROWS)
+#define PJ_PENDING (-1)
+
+struct PjSmem {
+    int cellEnd[2 * PJ_CELLS];      /* end of each cell's run in `sorted` (start = end of the cell before) */
+    int owner[PJ_MAXKP];
+    uint16_t sorted[PJ_MAXKP];
+    uint32_t taken[PJ_MAXKP / 4];   /* one byte per keypoint: bit 0 taken, bit 1 taken as of the next round */
+    int warpSum[PJ_NT / 32];
+};
+
+struct PjFrame {
+    const orbfe_keypoint* kps;
+    const uint4* desc;
+    const float* uRight;
+    const int32_t* partner;
+    int n, nLeft;
+    float minx, miny, invw, invh;
+};
+
+static __device__ __forceinline__ int pj_ham(const uint4 qa, const uint4 qb, const uint4 a, const uint4 b) {
+    return __popc(qa.x ^ a.x) + __popc(qa.y ^ a.y) + __popc(qa.z ^ a.z) + __popc(qa.w ^ a.w) + __popc(qb.x ^ b.x) + __popc(qb.y ^ b.y) +
+           __popc(qb.z ^ b.z) + __popc(qb.w ^ b.w);
+}
+
+/* Frame::GetFeaturesInArea: visit(row, octave) for every keypoint of the window, in the reference's order */
+template <class F>
+static __device__ __forceinline__ void pj_window(const PjFrame& fr, const PjSmem& s, const orbfe_proj_query& p, F&& visit) {
+    const float r = p.radius, ax = p.x - fr.minx, ay = p.y - fr.miny;
+    const int x0 = max(0, (int)floorf((ax - r) * fr.invw));
+    if (x0 >= PJ_COLS) return;
+    const int x1 = min(PJ_COLS - 1, (int)ceilf((ax + r) * fr.invw));
+    if (x1 < 0) return;
+    const int y0 = max(0, (int)floorf((ay - r) * fr.invh));
+    if (y0 >= PJ_ROWS) return;
+    const int y1 = min(PJ_ROWS - 1, (int)ceilf((ay + r) * fr.invh));
+    if (y1 < 0) return;
+    const int side = (p.flags & ORBFE_PQ_RIGHT) ? PJ_CELLS : 0;
+    for (int ix = x0; ix <= x1; ix++) {
+        const int c0 = side + ix * PJ_ROWS + y0, c1 = side + ix * PJ_ROWS + y1;
+        /* the cells iy = y0..y1 of one column are adjacent in the sort: one run */
+        const int beg = c0 ? s.cellEnd[c0 - 1] : 0, end = s.cellEnd[c1];
+        for (int j = beg; j < end; j++) {
+            const int row = s.sorted[j];
+            const orbfe_keypoint* kp = fr.kps + row;
+            const int oct = __ldg(&kp->octave);
+            if (oct < p.min_level || (p.max_level >= 0 && oct > p.max_level)) continue;
+            if (fabsf(__ldg(&kp->x) - p.x) < r && fabsf(__ldg(&kp->y) - p.y) < r) visit(row, oct);
+        }
+    }
+}
+
+__global__ void __launch_bounds__(PJ_NT) k_search_by_projection(int maxKp, const orbfe_keypoint* __restrict__ kpsAll, const uint8_t* __restrict__ descAll,
+                                                                const int32_t* __restrict__ kpOff, const int32_t* __restrict__ nLeftAll,
+                                                                const float* __restrict__ uRightAll, const int32_t* __restrict__ partnerAll,
+                                                                const uint8_t* __restrict__ takenIn, const orbfe_frame_grid* __restrict__ grids,
+                                                                const orbfe_proj_query* __restrict__ queries, const uint8_t* __restrict__ qdescAll,
+                                                                const int32_t* __restrict__ qOff, int thHigh, float nnratio, orbfe_proj_match* out,
+                                                                uint8_t* __restrict__ takenOut) {
+    extern __shared__ __align__(16) unsigned char pj_raw[];
+    PjSmem& s = *reinterpret_cast<PjSmem*>(pj_raw);
+    const int tid = threadIdx.x, f = blockIdx.x;
+    const int k0 = kpOff[f], q0 = qOff[f], nq = qOff[f + 1] - q0;
+    PjFrame fr;
+    fr.n = kpOff[f + 1] - k0;
+    fr.kps = kpsAll + k0;
+    fr.desc = reinterpret_cast<const uint4*>(descAll) + (size_t)k0 * 2;
+    fr.uRight = uRightAll ? uRightAll + k0 : nullptr;
+    fr.partner = partnerAll ? partnerAll + k0 : nullptr;
+    fr.nLeft = nLeftAll ? nLeftAll[f] : -1;
+    const orbfe_frame_grid g = grids[f];
+    fr.minx = g.min_x; fr.miny = g.min_y; fr.invw = g.inv_w; fr.invh = g.inv_h;
+    const orbfe_proj_query* qs = queries + q0;
+    const uint4* qdesc = reinterpret_cast<const uint4*>(qdescAll) + (size_t)q0 * 2;
+    orbfe_proj_match* res = out + q0;
+    volatile int* status = &res[0].status; /* stride 7 ints; PJ_PENDING while unresolved */
+
+    if (fr.n > maxKp || fr.n > PJ_MAXKP || fr.n < 0) { /* the caller's promise about the frame size does not hold */
+        for (int q = tid; q < nq; q += PJ_NT) {
+            orbfe_proj_match m;
+            m.best_idx = -1; m.best_dist = 256; m.best_level = -1; m.second_dist = 256; m.second_level = -1; m.accepted = 0; m.status = ORBFE_PS_CAPACITY;
+            res[q] = m;
+        }
+        return;
+    }
+    const bool gateRight = fr.nLeft < 0 && fr.uRight != nullptr;
+    const bool stereoRig = fr.nLeft >= 0 && fr.partner != nullptr;
+
+    /* ---- grid: AssignFeaturesToGrid as a counting sort ---- */
+    for (int i = tid; i < 2 * PJ_CELLS; i += PJ_NT) s.cellEnd[i] = 0;
+    for (int i = tid; i < PJ_MAXKP / 4; i += PJ_NT) s.taken[i] = 0;
+    __syncthreads();
+    uint8_t* takenB = reinterpret_cast<uint8_t*>(s.taken);
+    for (int i = tid; i < fr.n; i += PJ_NT) {
+        const float x = __ldg(&fr.kps[i].x), y = __ldg(&fr.kps[i].y);
+        const int px = (int)roundf((x - fr.minx) * fr.invw), py = (int)roundf((y - fr.miny) * fr.invh);
+        int c = -1;
+        if (px >= 0 && px < PJ_COLS && py >= 0 && py < PJ_ROWS) {
+            c = ((fr.nLeft >= 0 && i >= fr.nLeft) ? PJ_CELLS : 0) + px * PJ_ROWS + py;
+            atomicAdd(&s.cellEnd[c], 1);
+        }
+        s.owner[i] = c;
+        takenB[i] = (takenIn && takenIn[k0 + i]) ? 1 : 0;
+    }
+    __syncthreads();
+    {   /* exclusive scan of the 6144 counts: 24 consecutive cells per thread */
+        const int per = 2 * PJ_CELLS / PJ_NT, base = tid * per;
+        int sum = 0;
+        for (int i = 0; i < per; i++) sum += s.cellEnd[base + i];
+        int incl = sum;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, incl, o);
+            if ((tid & 31) >= o) incl += t;
+        }
+        if ((tid & 31) == 31) s.warpSum[tid >> 5] = incl;
+        __syncthreads();
+        int run = incl - sum;
+        for (int w = 0; w < (tid >> 5); w++) run += s.warpSum[w];
+        for (int i = 0; i < per; i++) {
+            const int c = s.cellEnd[base + i];
+            s.cellEnd[base + i] = run;
+            run += c;
+        }
+    }
+    __syncthreads();
+    for (int i = tid; i < fr.n; i += PJ_NT) {
+        const int c = s.owner[i];
+        if (c >= 0) s.sorted[atomicAdd(&s.cellEnd[c], 1)] = (uint16_t)i;   /* cellEnd[c] ends up as the end of cell c */
+    }
+    __syncthreads();
+    for (int c = tid; c < 2 * PJ_CELLS; c += PJ_NT) {   /* ascending rows inside each cell (the lists are a few entries long) */
+        const int beg = c ? s.cellEnd[c - 1] : 0, end = s.cellEnd[c];
+        for (int i = beg + 1; i < end; i++) {
+            const uint16_t v = s.sorted[i];
+            int j = i - 1;
+            while (j >= beg && s.sorted[j] > v) { s.sorted[j + 1] = s.sorted[j]; j--; }
+            s.sorted[j + 1] = v;
+        }
+    }
+    for (int q = tid; q < nq; q += PJ_NT) {
+        orbfe_proj_match m;
+        m.best_idx = -1; m.best_dist = 256; m.best_level = -1; m.second_dist = 256; m.second_level = -1; m.accepted = 0;
+        m.status = (qs[q].flags & ORBFE_PQ_SKIP) ? ORBFE_PS_SKIPPED : PJ_PENDING;
+        res[q] = m;
+    }
+    __syncthreads();
+
+    /* ---- rounds ---- */
+    for (;;) {
+        for (int i = tid; i < fr.n; i += PJ_NT) {
+            s.owner[i] = INT_MAX;
+            if (takenB[i] & 2) takenB[i] = 1;
+        }
+        __syncthreads();
+        /* A. stamps */
+        for (int q = tid; q < nq; q += PJ_NT) {
+            if (status[q * 7] != PJ_PENDING) continue;
+            const orbfe_proj_query p = qs[q];
+            if (p.flags & ORBFE_PQ_AFTER_LEFT) res[q].accepted = (q > 0 && status[(q - 1) * 7] == PJ_PENDING) ? 0 : 1;   /* may I look at q-1 in step B? */
+            pj_window(fr, s, p, [&](int row, int) {
+                if (takenB[row] & 1) return;
+                if (gateRight) {
+                    const float ur = __ldg(fr.uRight + row);
+                    if (ur > 0 && fabsf(p.xr - ur) > p.radius) return;
+                }
+                atomicMin(&s.owner[row], q);
+                if (stereoRig) {
+                    const int pt = __ldg(fr.partner + row);
+                    if (pt >= 0 && pt < fr.n) atomicMin(&s.owner[pt], q);
+                }
+            });
+        }
+        __syncthreads();
+        /* B. scan, decide */
+        int pending = 0;
+        for (int q = tid; q < nq; q += PJ_NT) {
+            if (status[q * 7] != PJ_PENDING) continue;
+            const orbfe_proj_query p = qs[q];
+            if (p.flags & ORBFE_PQ_AFTER_LEFT) {
+                if (res[q].accepted == 0) { pending++; continue; }
+                res[q].accepted = 0;
+                if (q > 0 && status[(q - 1) * 7] == ORBFE_PS_RATIO_REJECTED && !(qs[q - 1].flags & ORBFE_PQ_RIGHT)) {
+                    status[q * 7] = ORBFE_PS_DROPPED;   /* the `continue` of ORBmatcher.cc:117-118 skips this half too */
+                    continue;
+                }
+            }
+            const uint4 qa = __ldg(qdesc + 2 * q), qb = __ldg(qdesc + 2 * q + 1);
+            int bestDist = 256, bestLevel = -1, bestDist2 = 256, bestLevel2 = -1, bestIdx = -1;
+            pj_window(fr, s, p, [&](int row, int oct) {
+                if (takenB[row] & 1) return;
+                if (gateRight) {
+                    const float ur = __ldg(fr.uRight + row);
+                    if (ur > 0 && fabsf(p.xr - ur) > p.radius) return;
+                }
+                const int dist = pj_ham(qa, qb, __ldg(fr.desc + 2 * row), __ldg(fr.desc + 2 * row + 1));
+                if (dist < bestDist) { bestDist2 = bestDist; bestDist = dist; bestLevel2 = bestLevel; bestLevel = oct; bestIdx = row; }
+                else if (dist < bestDist2) { bestLevel2 = oct; bestDist2 = dist; }
+            });
+            int st = ORBFE_PS_NO_CANDIDATES;
+            bool blocked = false;
+            int partnerRow = -1;
+            if (bestIdx >= 0) {
+                st = bestDist > thHigh ? ORBFE_PS_OVER_THRESHOLD
+                     : (bestLevel == bestLevel2 && (float)bestDist > nnratio * (float)bestDist2) ? ORBFE_PS_RATIO_REJECTED : ORBFE_PS_ACCEPTED;
+                pj_window(fr, s, p, [&](int row, int) {
+                    if (blocked || (takenB[row] & 1)) return;
+                    if (gateRight) {
+                        const float ur = __ldg(fr.uRight + row);
+                        if (ur > 0 && fabsf(p.xr - ur) > p.radius) return;
+                    }
+                    if (s.owner[row] < q && pj_ham(qa, qb, __ldg(fr.desc + 2 * row), __ldg(fr.desc + 2 * row + 1)) <= bestDist2) blocked = true;
+                });
+                if (st == ORBFE_PS_ACCEPTED && stereoRig) {
+                    const int pt = __ldg(fr.partner + bestIdx);
+                    if (pt >= 0 && pt < fr.n) { partnerRow = pt; if (s.owner[pt] < q) blocked = true; }
+                }
+            }
+            if (blocked) { pending++; continue; }
+            orbfe_proj_match m;
+            m.best_idx = bestIdx; m.best_dist = bestDist; m.best_level = bestLevel; m.second_dist = bestDist2; m.second_level = bestLevel2;
+            m.accepted = st == ORBFE_PS_ACCEPTED ? 1 : 0; m.status = st;
+            res[q] = m;
+            if (st == ORBFE_PS_ACCEPTED && (p.flags & ORBFE_PQ_BLOCKS)) {
+                atomicOr(&s.taken[bestIdx >> 2], 2u << (8 * (bestIdx & 3)));
+                if (partnerRow >= 0) atomicOr(&s.taken[partnerRow >> 2], 2u << (8 * (partnerRow & 3)));
+            }
+        }
+        if (__syncthreads_count(pending) == 0) break;
+    }
+    if (takenOut)
+        for (int i = tid; i < fr.n; i += PJ_NT) takenOut[k0 + i] = takenB[i] ? 1 : 0;
+}
+
+extern "C" {
+
+int orbfe_search_by_projection_device(int device, int nframes, int max_keypoints, const orbfe_keypoint* d_kps, const uint8_t* d_desc,
+                                      const int32_t* d_kp_offsets, const int32_t* d_n_left, const float* d_u_right, const int32_t* d_partner,
+                                      const uint8_t* d_taken_in, const orbfe_frame_grid* d_grids, const orbfe_proj_query* d_queries,
+                                      const uint8_t* d_qdesc, const int32_t* d_q_offsets, int th_high, float nnratio, orbfe_proj_match* d_out,
+                                      uint8_t* d_taken_out, void* stream) {
+    if (nframes < 1 || !d_kps || !d_desc || !d_kp_offsets || !d_grids || !d_queries || !d_qdesc || !d_q_offsets || !d_out) { orbfe_set_error("bad argument"); return ORBFE_E_INVALID; }
+    if (max_keypoints < 0 || max_keypoints > PJ_MAXKP) { orbfe_set_error("at most %d keypoints per frame (both cameras together)", PJ_MAXKP); return ORBFE_E_CAPACITY; }
+    if (((uintptr_t)d_desc | (uintptr_t)d_qdesc) & 15) { orbfe_set_error("descriptor arrays must be 16-byte aligned"); return ORBFE_E_INVALID; }
+    ORBFE_CUDA(cudaSetDevice(device));
+    static thread_local int configured = -1;
+    if (configured != device) {
+        ORBFE_CUDA(cudaFuncSetAttribute(k_search_by_projection, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(PjSmem)));
+        configured = device;
+    }
+    k_search_by_projection<<<nframes, PJ_NT, sizeof(PjSmem), (cudaStream_t)stream>>>(max_keypoints, d_kps, d_desc, d_kp_offsets, d_n_left, d_u_right, d_partner,
+                                                                                    d_taken_in, d_grids, d_queries, d_qdesc, d_q_offsets, th_high, nnratio,
+                                                                                    d_out, d_taken_out);
+    ORBFE_CUDA(cudaGetLastError());
+    return ORBFE_OK;
+}
+
+int orbfe_search_by_projection(int device, const orbfe_keypoint* kps, const uint8_t* desc, int n, int n_left, const float* u_right, const int32_t* partner,
+                               uint8_t* taken, const orbfe_frame_grid* grid, const orbfe_proj_query* queries, const uint8_t* qdesc, int nq, int th_high,
+                               float nnratio, orbfe_proj_match* out, int* nmatches) {
+    if (!kps || !desc || !grid || !queries || !qdesc || !out || n < 0 || nq < 0) { orbfe_set_error("bad argument"); return ORBFE_E_INVALID; }
+    if (n > PJ_MAXKP) { orbfe_set_error("at most %d keypoints per frame (both cameras together)", PJ_MAXKP); return ORBFE_E_CAPACITY; }
+    if (nmatches) *nmatches = 0;
+    if (nq == 0) return ORBFE_OK;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev) {
+        orbfe_set_error("no usable CUDA device %d (found %d); this library has no CPU path", device, ndev);
+        return ORBFE_E_CUDA;
+    }
+    ORBFE_CUDA(cudaSetDevice(device));
+    /* one staging block: [kps | desc | qdesc | queries | out | uRight | partner | taken | grid | offsets | nLeft] */
+    size_t off = 0;
+    auto take = [&](size_t bytes) { const size_t o = off; off += (bytes + 255) & ~(size_t)255; return o; };
+    const size_t oKps = take((size_t)n * sizeof(orbfe_keypoint)), oDesc = take((size_t)n * 32), oQd = take((size_t)nq * 32);
+    const size_t oQ = take((size_t)nq * sizeof(orbfe_proj_query)), oOut = take((size_t)nq * sizeof(orbfe_proj_match));
+    const size_t oUr = take((size_t)n * 4), oPt = take((size_t)n * 4), oTk = take((size_t)n), oGrid = take(sizeof(orbfe_frame_grid)), oOff = take(5 * sizeof(int32_t));
+    uint8_t* d = nullptr;
+    ORBFE_CUDA(cudaMalloc((void**)&d, off));
+    cudaStream_t st = nullptr;
+    const int32_t offs[5] = {0, n, 0, nq, n_left};
+    cudaError_t e = cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking);
+#define PJ_UP(dst, src, bytes) if (e == cudaSuccess && (bytes) > 0) e = cudaMemcpyAsync(d + (dst), (src), (bytes), cudaMemcpyHostToDevice, st)
+    PJ_UP(oKps, kps, (size_t)n * sizeof(orbfe_keypoint));
+    PJ_UP(oDesc, desc, (size_t)n * 32);
+    PJ_UP(oQd, qdesc, (size_t)nq * 32);
+    PJ_UP(oQ, queries, (size_t)nq * sizeof(orbfe_proj_query));
+    if (u_right) PJ_UP(oUr, u_right, (size_t)n * 4);
+    if (partner) PJ_UP(oPt, partner, (size_t)n * 4);
+    if (taken) PJ_UP(oTk, taken, (size_t)n);
+    PJ_UP(oGrid, grid, sizeof(orbfe_frame_grid));
+    PJ_UP(oOff, offs, sizeof(offs));
+#undef PJ_UP
+    int rc = ORBFE_OK;
+    if (e == cudaSuccess)
+        rc = orbfe_search_by_projection_device(device, 1, PJ_MAXKP, (const orbfe_keypoint*)(d + oKps), d + oDesc, (const int32_t*)(d + oOff),
+                                               (const int32_t*)(d + oOff) + 4, u_right ? (const float*)(d + oUr) : nullptr,
+                                               partner ? (const int32_t*)(d + oPt) : nullptr, taken ? d + oTk : nullptr, (const orbfe_frame_grid*)(d + oGrid),
+                                               (const orbfe_proj_query*)(d + oQ), d + oQd, (const int32_t*)(d + oOff) + 2, th_high, nnratio,
+                                               (orbfe_proj_match*)(d + oOut), taken ? d + oTk : nullptr, st);
+    if (rc == ORBFE_OK && e == cudaSuccess) e = cudaMemcpyAsync(out, d + oOut, (size_t)nq * sizeof(orbfe_proj_match), cudaMemcpyDeviceToHost, st);
+    if (rc == ORBFE_OK && e == cudaSuccess && taken && n > 0) e = cudaMemcpyAsync(taken, d + oTk, (size_t)n, cudaMemcpyDeviceToHost, st);
+    if (rc == ORBFE_OK && e == cudaSuccess) e = cudaStreamSynchronize(st);
+    if (st) cudaStreamDestroy(st);
+    cudaFree(d);
+    if (rc != ORBFE_OK) return rc;
+    if (e != cudaSuccess) return orbfe_cuda_fail(e, "search_by_projection");
+    if (nmatches) {
+        int c = 0;
+        for (int i = 0; i < nq; i++)
+            if (out[i].accepted) c += 1 + ((n_left >= 0 && partner && partner[out[i].best_idx] >= 0) ? 1 : 0);
+        *nmatches = c;
+    }
+    return ORBFE_OK;
+}
+
+}  /* extern "C" */

@@ -1,0 +1,107 @@
+"""Seeded inputs for the projection-gated search, shared by tools/make_goldens.py, the tests and bench.py.
+A case is a dict of arrays in the layouts of include/orbfe.h (orbfe_keypoint, orbfe_proj_query, ...)."""
+import numpy as np
+
+KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"), ("response", "<f4"), ("octave", "<i4"), ("class_id", "<i4")])
+PROJ_QUERY_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("radius", "<f4"), ("xr", "<f4"), ("min_level", "<i4"), ("max_level", "<i4"), ("flags", "<i4")])
+PQ_RIGHT, PQ_BLOCKS, PQ_SKIP, PQ_AFTER_LEFT = 1, 2, 4, 8
+
+
+def _flip(rng, d, k):
+    d = d.copy()
+    for b in rng.choice(256, size=k, replace=False):
+        d[b >> 3] ^= np.uint8(1 << (b & 7))
+    return d
+
+
+def make_case(seed, n=600, nq=700, W=752, H=480, th=1.0, fisheye=False, stereo_gate=False, crowd=0.0):
+    """crowd: fraction of the map points aimed at a small set of keypoints (long chains of map points competing for the same
+    keypoints); th: the search-window factor of SearchByProjection."""
+    rng = np.random.RandomState(seed)
+    f32 = np.float32
+    kps = np.zeros(n, KP_DTYPE)
+    kps["x"] = rng.uniform(-4, W + 4, n).astype(f32)          # a few fall outside the image bounds (PosInGrid drops them)
+    kps["y"] = rng.uniform(-4, H + 4, n).astype(f32)
+    # clusters: a third of the keypoints sit within a few pixels of another one
+    src = rng.randint(0, n, n // 3)
+    dst = rng.choice(n, n // 3, replace=False)
+    kps["x"][dst] = kps["x"][src] + rng.uniform(-3, 3, n // 3).astype(f32)
+    kps["y"][dst] = kps["y"][src] + rng.uniform(-3, 3, n // 3).astype(f32)
+    kps["octave"] = np.minimum(rng.geometric(0.3, n) - 1, 7)
+    kps["size"] = 31
+    kps["class_id"] = -1
+    desc = rng.randint(0, 256, (n, 32)).astype(np.uint8)
+    desc[dst[: n // 8]] = desc[src[: n // 8]]                   # exact descriptor duplicates next to each other: distance ties
+    n_left = -1
+    if fisheye:
+        n_left = n // 2 + 7
+    case = {"kps": kps, "desc": desc, "n_left": np.array([n_left], np.int32),
+            "grid": np.array([0, 0, f32(64) / f32(W), f32(48) / f32(H)], f32), "th_high": np.array([100], np.int32),
+            "nnratio": np.array([0.8], f32), "taken": (rng.uniform(size=n) < 0.08).astype(np.uint8)}
+    if stereo_gate:
+        ur = kps["x"] - rng.uniform(1, 40, n).astype(f32)
+        ur[rng.uniform(size=n) < 0.4] = -1
+        case["u_right"] = ur.astype(f32)
+    if fisheye:
+        partner = np.full(n, -1, np.int32)
+        nl, nr = n_left, n - n_left
+        for _ in range(nl // 2):                               # like ComputeStereoFishEyeMatches: later matches overwrite one side
+            a, b = rng.randint(0, nl), rng.randint(0, nr)
+            partner[a] = nl + b
+            partner[nl + b] = a
+        case["partner"] = partner
+    scale = np.array([f32(1.2) ** i for i in range(8)], f32)
+    hot = rng.choice(n, min(n, max(4, n // 40)), replace=False)
+    q = []
+    qd = []
+    count = 0
+    while count < nq:
+        aimed = rng.uniform() < 0.75
+        if aimed:
+            t = int(hot[rng.randint(len(hot))]) if rng.uniform() < crowd else int(rng.randint(n))
+            lvl = int(min(7, kps["octave"][t] + rng.randint(0, 2)))
+            r = f32(2.5 if rng.uniform() < 0.5 else 4.0) * f32(th) * scale[lvl]
+            x = f32(kps["x"][t] + rng.uniform(-0.7, 0.7) * r)
+            y = f32(kps["y"][t] + rng.uniform(-0.7, 0.7) * r)
+            d = _flip(rng, desc[t], int(rng.randint(0, 75)))
+        else:
+            t = -1
+            lvl = int(rng.randint(0, 8))
+            r = f32(2.5 if rng.uniform() < 0.5 else 4.0) * f32(th) * scale[lvl]
+            x, y = f32(rng.uniform(-30, W + 30)), f32(rng.uniform(-30, H + 30))
+            d = rng.randint(0, 256, 32).astype(np.uint8)
+        flags = PQ_BLOCKS if rng.uniform() < 0.9 else 0
+        if rng.uniform() < 0.05:
+            flags |= PQ_SKIP
+        xr = f32(x - rng.uniform(1, 40))
+        if stereo_gate and t >= 0 and case["u_right"][t] > 0:
+            xr = f32(case["u_right"][t] + rng.uniform(-1.3, 1.3) * r)
+        minl, maxl = lvl - 1, lvl
+        if rng.uniform() < 0.03:
+            minl, maxl = 0, -1                                  # bCheckLevels == false
+        if fisheye:
+            right_target = t >= n_left
+            # left-camera half, then (for most points) the right-camera half of the same map point
+            q.append((x, y, r, xr, minl, maxl, flags | (PQ_RIGHT if right_target and rng.uniform() < 0.5 else 0)))
+            qd.append(d)
+            count += 1
+            if not (q[-1][6] & PQ_RIGHT) and rng.uniform() < 0.7:
+                q.append((f32(x + rng.uniform(-2, 2)), f32(y + rng.uniform(-2, 2)), r, xr, minl, maxl, flags | PQ_RIGHT | PQ_AFTER_LEFT))
+                qd.append(d)
+                count += 1
+        else:
+            q.append((x, y, r, xr, minl, maxl, flags))
+            qd.append(d)
+            count += 1
+    case["queries"] = np.array(q, PROJ_QUERY_DTYPE)
+    case["qdesc"] = np.stack(qd).astype(np.uint8)
+    return case
+
+
+CASES = {
+    # name: make_case arguments
+    "mono": dict(seed=11, n=600, nq=700),
+    "stereo_gate": dict(seed=12, n=800, nq=900, stereo_gate=True),
+    "wide": dict(seed=13, n=500, nq=600, th=3.0, crowd=0.5),
+    "fisheye": dict(seed=14, n=900, nq=800, fisheye=True, th=1.5, crowd=0.3),
+}

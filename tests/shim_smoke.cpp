@@ -24,10 +24,22 @@ int main(int argc, char** argv) {
     ORBmatcher m(0.9f, true);
     std::vector<orbfe_match> res;
     const int acc = m.SearchTop2(dL, dR, res);
+    // Tracking::SearchLocalPoints-like: every left keypoint re-projected half a pixel off as a map point (src/ORBmatcher.cc:44-214)
+    std::vector<orbfe_proj_query> pq(kL.size());
+    for (size_t i = 0; i < kL.size(); i++) {
+        pq[i].x = kL[i].pt.x + 0.5f; pq[i].y = kL[i].pt.y - 0.5f;
+        pq[i].radius = 4.0f * left.GetScaleFactors()[kL[i].octave];
+        pq[i].xr = uR[i]; pq[i].min_level = kL[i].octave - 1; pq[i].max_level = kL[i].octave; pq[i].flags = ORBFE_PQ_BLOCKS;
+    }
+    std::vector<unsigned char> taken;
+    std::vector<orbfe_proj_match> pm;
+    const int proj = SearchByProjection(kL, dL, -1, &uR, nullptr, taken, 0.f, 0.f, 64.f / W, 48.f / H, pq, dL, 0.8f, pm);
+    int projSelf = 0;
+    for (size_t i = 0; i < pm.size(); i++) projSelf += pm[i].accepted && pm[i].best_idx == (int)i;
     cv::Mat empty;
     const int rcEmpty = left(empty, mask, kR, dR, lap);
-    printf("shim n=%zu mono=%d monoR=%d levels=%d pyr0=%dx%d stereo=%d d01=%d top2acc=%d empty=%d first=(%.1f,%.1f,%.3f,%d)\n",
-           kL.size(), monoL, monoR, left.GetLevels(), left.mvImagePyramid[0].cols, left.mvImagePyramid[0].rows, matched, d01, acc, rcEmpty,
+    printf("shim n=%zu mono=%d monoR=%d levels=%d pyr0=%dx%d stereo=%d d01=%d top2acc=%d proj=%d projself=%d empty=%d first=(%.1f,%.1f,%.3f,%d)\n",
+           kL.size(), monoL, monoR, left.GetLevels(), left.mvImagePyramid[0].cols, left.mvImagePyramid[0].rows, matched, d01, acc, proj, projSelf, rcEmpty,
            kL[0].pt.x, kL[0].pt.y, kL[0].angle, kL[0].octave);
     return 0;
 }

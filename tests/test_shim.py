@@ -38,5 +38,13 @@ def test_shim_matches_oracle(tmp_path):
     assert int(f["stereo"]) == kept
     assert int(f["d01"]) == O.descriptor_distance(dL[0], dL[1])
     assert int(f["top2acc"]) == int(top2["accepted"].sum())
+    pq = np.zeros(len(kL), O.PROJ_QUERY_DTYPE)
+    scale = np.asarray(oL.scale_factors(), np.float32)[kL["octave"]]
+    pq["x"], pq["y"], pq["radius"], pq["xr"] = kL["x"] + np.float32(0.5), kL["y"] - np.float32(0.5), np.float32(4.0) * scale, u
+    pq["min_level"], pq["max_level"], pq["flags"] = kL["octave"] - 1, kL["octave"], 2
+    grid = np.array([0, 0, np.float32(64) / np.float32(752), np.float32(48) / np.float32(480)], np.float32)
+    pm, _, nm = O.search_by_projection(kL, dL, pq, dL, grid, u_right=u, nnratio=0.8)
+    assert int(f["proj"]) == nm and int(f["projself"]) == int(((pm["best_idx"] == np.arange(len(kL))) & (pm["accepted"] == 1)).sum())
+    assert nm > 1000
     first = "(%.1f,%.1f,%.3f,%d)" % (kL[0]["x"], kL[0]["y"], kL[0]["angle"], kL[0]["octave"])
     assert f["first"] == first

@@ -375,6 +375,86 @@ CASES = [
 ]
 
 
+def py_search_by_projection(c):
+    """Independent restatement (plain Python, written from /root/reference/src/ORBmatcher.cc:44-214 and src/Frame.cc:380-411,
+    643-721, not from oracle/project_oracle.cpp) of the projection-gated search on a synth/projection_cases.py case."""
+    kps, desc, q, qd = c["kps"], c["desc"], c["queries"], c["qdesc"]
+    n, nleft = len(kps), int(c["n_left"][0])
+    minx, miny, invw, invh = [f32(v) for v in c["grid"]]
+    ur, partner = c.get("u_right"), c.get("partner")
+    taken = c["taken"].astype(bool).copy()
+    th_high, ratio = int(c["th_high"][0]), f32(c["nnratio"][0])
+    popc = np.array([bin(i).count("1") for i in range(256)], np.int32)
+    cells = {}
+    for i in range(n):
+        px = (f32(kps["x"][i]) - minx) * invw
+        py = (f32(kps["y"][i]) - miny) * invh
+        cx, cy = int(math.floor(abs(px) + 0.5) * (1 if px >= 0 else -1)), int(math.floor(abs(py) + 0.5) * (1 if py >= 0 else -1))   # C round()
+        if 0 <= cx < 64 and 0 <= cy < 48:
+            cells.setdefault((1 if (nleft >= 0 and i >= nleft) else 0, cx, cy), []).append(i)
+    res = np.zeros((len(q), 7), np.int32)
+    nmatches = 0
+    skip_right_half = False
+    for k in range(len(q)):
+        x, y, r, xr = f32(q["x"][k]), f32(q["y"][k]), f32(q["radius"][k]), f32(q["xr"][k])
+        minl, maxl, flags = int(q["min_level"][k]), int(q["max_level"][k]), int(q["flags"][k])
+        res[k] = (-1, 256, -1, 256, -1, 0, 0)
+        drop = bool(flags & 8) and skip_right_half
+        skip_right_half = False
+        if flags & 4:
+            res[k, 6] = 4
+            continue
+        if drop:
+            res[k, 6] = 6
+            continue
+        side = 1 if flags & 1 else 0
+        cand = []
+        x0 = max(0, int(math.floor((x - minx - r) * invw)))
+        x1 = min(63, int(math.ceil((x - minx + r) * invw)))
+        y0 = max(0, int(math.floor((y - miny - r) * invh)))
+        y1 = min(47, int(math.ceil((y - miny + r) * invh)))
+        if x0 < 64 and x1 >= 0 and y0 < 48 and y1 >= 0:
+            for ix in range(x0, x1 + 1):
+                for iy in range(y0, y1 + 1):
+                    for i in cells.get((side, ix, iy), []):
+                        o = int(kps["octave"][i])
+                        if (minl > 0 or maxl >= 0) and (o < minl or (maxl >= 0 and o > maxl)):
+                            continue
+                        if abs(f32(kps["x"][i]) - x) < r and abs(f32(kps["y"][i]) - y) < r:
+                            cand.append(i)
+        best, blvl, best2, blvl2, bidx = 256, -1, 256, -1, -1
+        for i in cand:
+            if taken[i]:
+                continue
+            if nleft < 0 and ur is not None and ur[i] > 0 and abs(xr - f32(ur[i])) > r:
+                continue
+            d = int(popc[desc[i] ^ qd[k]].sum())
+            if d < best:
+                best2, blvl2 = best, blvl
+                best, blvl, bidx = d, int(kps["octave"][i]), i
+            elif d < best2:
+                best2, blvl2 = d, int(kps["octave"][i])
+        res[k, :5] = (bidx, best, blvl, best2, blvl2)
+        if bidx < 0:
+            continue
+        if best > th_high:
+            res[k, 6] = 2
+            continue
+        if blvl == blvl2 and f32(best) > ratio * f32(best2):
+            res[k, 6] = 3
+            skip_right_half = not side
+            continue
+        res[k, 5], res[k, 6] = 1, 1
+        nmatches += 1
+        if flags & 2:
+            taken[bidx] = True
+        if nleft >= 0 and partner is not None and partner[bidx] >= 0:
+            nmatches += 1
+            if flags & 2:
+                taken[partner[bidx]] = True
+    return res, taken.astype(np.uint8), nmatches
+
+
 def main():
     out_dir = os.path.join(ROOT, "tests", "golden")
     os.makedirs(out_dir, exist_ok=True)
@@ -484,6 +564,19 @@ def main():
     c2 = cv2.createCLAHE(clipLimit=40.0, tileGridSize=(4, 6))
     cond["clahe_out_d"] = c2.apply(cond["clahe_src_a"])   # other parameters: clip 40, 4 x 6 tiles (cv::Size(4, 6): 4 across)
     np.savez_compressed(os.path.join(out_dir, "conditioning.npz"), **cond)
+    # projection-gated search: inputs from synth/projection_cases.py, expected output from the Python restatement
+    from orb_slam3_detailed_comments_kor_b200.synth import projection_cases
+    proj = {}
+    for name, kw in projection_cases.CASES.items():
+        c = projection_cases.make_case(**kw)
+        res, taken, nm = py_search_by_projection(c)
+        for k, v in c.items():
+            proj[name + "/" + k] = v
+        proj[name + "/expect"] = res
+        proj[name + "/taken_after"] = taken
+        proj[name + "/nmatches"] = np.array([nm], np.int32)
+        print("projection", name, "nmatches", nm, "accepted", int(res[:, 5].sum()))
+    np.savez_compressed(os.path.join(out_dir, "projection.npz"), **proj)
     print("wrote goldens to", out_dir, "cv2", cv2.__version__)
 
 
