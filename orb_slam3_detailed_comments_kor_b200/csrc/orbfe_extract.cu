@@ -30,35 +30,23 @@ static __device__ __forceinline__ int reflect101(int p, int n) {
 }
 
 /* ------------------------------------------------------------------------------------------------ pyramid */
-/* Level 0: copyMakeBorder(image, 19, REFLECT_101) (src/ORBextractor.cc:1170-1173).  One thread = one 16-byte chunk
- * of a padded row; chunks that lie inside the image and are 16-byte aligned in the source move as one 128-bit
- * load/store, the others (borders, odd widths) go byte by byte through the reflected coordinate. */
+/* Level 0: the interior of copyMakeBorder(image, 19, REFLECT_101) (src/ORBextractor.cc:1170-1173).  One thread = one
+ * 16-byte chunk of an image row: a 128-bit load/store when the chunk is whole and the source is 16-byte aligned, byte by
+ * byte otherwise (odd widths, unaligned inputs).  The border comes from k_pyramid_fringe / k_pyramid_borders. */
 __global__ void __launch_bounds__(256) k_pyramid_copy0(const __grid_constant__ ExDesc d, ExBuffers b, const uint8_t* __restrict__ input) {
     const LevelDesc& L = d.lv[0];
-    const int chunks = L.pitch >> 4;
-    const int rows = L.h + 2 * ORBFE_EDGE;
+    const int chunks = (L.w + 15) >> 4;
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= chunks * rows) return;
-    const int row = idx / chunks, chunk = idx - row * chunks;
+    if (idx >= chunks * L.h) return;
+    const int row = idx / chunks, px0 = (idx - row * chunks) * 16;
     const size_t f = blockIdx.y;
-    const int yi = reflect101(row - ORBFE_EDGE, L.h);
-    const int px0 = chunk * 16 - ORBFE_ROW_LEAD;
-    const uint8_t* src = input + f * (size_t)d.W * d.H + (size_t)yi * d.W;
-    uint4 o;
-    if (px0 >= 0 && px0 + 16 <= L.w && ((reinterpret_cast<uintptr_t>(src + px0) & 15) == 0)) {
-        o = __ldg(reinterpret_cast<const uint4*>(src + px0));
+    const uint8_t* src = input + f * (size_t)d.W * d.H + (size_t)row * d.W + px0;
+    uint8_t* dst = b.pyr + f * d.pyrSlab + L.pyrOff + (size_t)(row + ORBFE_EDGE) * L.pitch + ORBFE_ROW_LEAD + px0;
+    if (px0 + 16 <= L.w && ((reinterpret_cast<uintptr_t>(src) & 15) == 0)) {
+        *reinterpret_cast<uint4*>(dst) = __ldg(reinterpret_cast<const uint4*>(src));
     } else {
-        uint32_t out[4] = {0, 0, 0, 0};
-#pragma unroll
-        for (int k = 0; k < 16; k++) {
-            const int px = px0 + k;
-            uint32_t v = 0;
-            if (px >= -ORBFE_EDGE && px < L.w + ORBFE_EDGE) v = __ldg(src + reflect101(px, L.w));
-            out[k >> 2] |= v << (8 * (k & 3));
-        }
-        o = make_uint4(out[0], out[1], out[2], out[3]);
+        for (int k = 0; k < 16 && px0 + k < L.w; k++) dst[k] = __ldg(src + k);
     }
-    *reinterpret_cast<uint4*>(b.pyr + f * d.pyrSlab + L.pyrOff + (size_t)row * L.pitch + chunk * 16) = o;
 }
 
 /* Levels >= 1: cv::resize(INTER_LINEAR) from the level below + copyMakeBorder in one pass
@@ -129,11 +117,54 @@ __global__ void __launch_bounds__(256) k_pyramid_level(const __grid_constant__ E
     }
 }
 
-/* REFLECT_101 border of levels >= 1 (copyMakeBorder, src/ORBextractor.cc:1167-1168), all levels in one launch
- * (gridDim.y = level - 1).  One thread = one 4-byte group that is not a full interior group.  A border pixel is a copy
- * of the interior pixel it mirrors (all interior pixels are final when this kernel starts). */
+/* The part of the REFLECT_101 border that the extractor itself reads: the Gaussian blur reaches 3 px past the image edge,
+ * nothing else leaves the interior (FAST stays 16 px inside, the orientation patch and the descriptor taps stay inside by
+ * construction, the next level's resize gives border pixels weight 0).  Per level: the word left of every interior row, the
+ * word(s) holding px w .. w+2 right of it, and three rows above and below over that same span.  One thread = one 4-byte
+ * group; all levels in one launch (gridDim.y = level).  The full 19 px border of the public pyramid
+ * (ORBextractor::mvImagePyramid lives in it) is written by k_pyramid_borders when somebody asks for it. */
+#define FRINGE 3
+__global__ void __launch_bounds__(128) k_pyramid_fringe(const __grid_constant__ ExDesc d, ExBuffers b) {
+    const int level = blockIdx.y;
+    const LevelDesc& L = d.lv[level];
+    const int gRight0 = L.w >> 2;                                 /* first group with a pixel >= w (or the partial one) */
+    const int gRight1 = (L.w + FRINGE - 1) >> 2;                  /* last group with a pixel <= w+2 */
+    const int nRight = gRight1 - gRight0 + 1, side = 1 + nRight;  /* fringe groups of an interior row */
+    const int span = gRight1 + 2;                                 /* groups -1 .. gRight1 of a band row */
+    int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    int row, g;                                                   /* interior row coordinate, group index (px = 4g) */
+    if (idx < L.h * side) {
+        row = idx / side;
+        const int j = idx - row * side;
+        g = j == 0 ? -1 : gRight0 + j - 1;
+    } else {
+        idx -= L.h * side;
+        if (idx >= 2 * FRINGE * span) return;
+        const int r = idx / span;
+        g = idx - r * span - 1;
+        row = r < FRINGE ? r - FRINGE : L.h + r - FRINGE;
+    }
+    uint8_t* slab = b.pyr + (size_t)blockIdx.z * d.pyrSlab;
+    uint8_t* lint = slab + (uint32_t)(L.pyrOff + ORBFE_EDGE * L.pitch + ORBFE_ROW_LEAD);   /* this level, interior (0,0) */
+    const uint8_t* srow = lint + reflect101(row, L.h) * L.pitch;
+    const int px0 = g * 4;
+    uint32_t out;
+    if (px0 >= 0 && px0 + 4 <= L.w) {
+        out = *reinterpret_cast<const uint32_t*>(srow + px0);
+    } else {
+        out = 0;
+#pragma unroll
+        for (int k = 0; k < 4; k++) out |= (uint32_t)srow[reflect101(px0 + k, L.w)] << (8 * k);   /* |overshoot| <= 4 */
+    }
+    *reinterpret_cast<uint32_t*>(lint + row * L.pitch + px0) = out;
+}
+
+/* The whole REFLECT_101 border (copyMakeBorder, src/ORBextractor.cc:1167-1168, 1172-1173), all levels in one launch
+ * (gridDim.y = level).  One thread = one 4-byte group that is not a full interior group.  A border pixel is a copy
+ * of the interior pixel it mirrors (all interior pixels are final when this kernel starts).  Not on the extraction path:
+ * launched by orbfe_materialize_borders for the callers that read the padded pyramid. */
 __global__ void __launch_bounds__(256) k_pyramid_borders(const __grid_constant__ ExDesc d, ExBuffers b) {
-    const int level = blockIdx.y + 1;
+    const int level = blockIdx.y;
     const LevelDesc& L = d.lv[level];
     const int G = L.pitch >> 2, nInt = L.w >> 2, gFirst = ORBFE_ROW_LEAD / 4;
     const int side = G - nInt;                                  /* border groups of an interior row */
@@ -1274,18 +1305,26 @@ int orbfe_launch_extract(orbfe_extractor* ex, const uint8_t* d_images, int nfram
     STAGE_MARK();
     {
         const LevelDesc& L = d.lv[0];
-        const int items = (L.pitch >> 4) * (L.h + 2 * ORBFE_EDGE);
+        const int items = ((L.w + 15) >> 4) * L.h;
         k_pyramid_copy0<<<dim3((items + 255) / 256, nframes), 256, 0, st>>>(d, xb, d_images);
     }
-    int maxBorder = 0;
     for (int l = 1; l < d.nlevels; l++) {
         const LevelDesc& L = d.lv[l];
-        const int nInt = L.w >> 2, G = L.pitch >> 2;
         k_pyramid_level<<<dim3(((L.w + 3) / 4 + 31) / 32, (L.h + 8 * PYR_ROWS - 1) / (8 * PYR_ROWS), nframes), dim3(32, 8), 0, st>>>(
             d, xb, ResizeArgs{L.w, L.h, L.pitch, L.pyrOff, d.lv[l - 1].pitch, d.lv[l - 1].pyrOff, L.tabX, L.tabY});
-        maxBorder = maxBorder > 2 * ORBFE_EDGE * G + L.h * (G - nInt) ? maxBorder : 2 * ORBFE_EDGE * G + L.h * (G - nInt);
     }
-    if (d.nlevels > 1) k_pyramid_borders<<<dim3((maxBorder + 255) / 256, d.nlevels - 1, nframes), 256, 0, st>>>(d, xb);
+    {
+        int items = 0;
+        for (int l = 0; l < d.nlevels; l++) {
+            const LevelDesc& L = d.lv[l];
+            const int n = L.h * (2 + ((L.w + FRINGE - 1) >> 2) - (L.w >> 2)) + 2 * FRINGE * (((L.w + FRINGE - 1) >> 2) + 2);
+            items = items > n ? items : n;
+        }
+        k_pyramid_fringe<<<dim3((items + 127) / 128, d.nlevels, nframes), 128, 0, st>>>(d, xb);
+    }
+    if (frame0 == 0) ex->batchFrames = 0;
+    ex->batchFrames = ex->batchFrames > frame0 + nframes ? ex->batchFrames : frame0 + nframes;
+    ex->bordersValid = 0;
     STAGE_MARK();
     {
         const bool few = nframes < 8;   /* few frames: the 16-row cut puts three times as many warps in flight */
@@ -1305,8 +1344,24 @@ int orbfe_launch_extract(orbfe_extractor* ex, const uint8_t* d_images, int nfram
     STAGE_MARK();
 #undef STAGE_MARK
     if (prof) ex->stagePending = 1;
-    ex->launches += d.nlevels + 7 + (d.nlevels > 1 ? 1 : 0);
+    ex->launches += d.nlevels + 8;
     ORBFE_CUDA(cudaGetLastError());
+    return 0;
+}
+
+/* The full 19 px border of every level of the frames of the last batch (idempotent; cleared by the next extraction). */
+int orbfe_materialize_borders(orbfe_extractor* ex, cudaStream_t st) {
+    if (ex->bordersValid || ex->batchFrames <= 0) return 0;
+    const ExDesc& d = ex->d;
+    int maxBorder = 0;
+    for (int l = 0; l < d.nlevels; l++) {
+        const LevelDesc& L = d.lv[l];
+        const int nInt = L.w >> 2, G = L.pitch >> 2, items = 2 * ORBFE_EDGE * G + L.h * (G - nInt);
+        maxBorder = maxBorder > items ? maxBorder : items;
+    }
+    k_pyramid_borders<<<dim3((maxBorder + 255) / 256, d.nlevels, ex->batchFrames), 256, 0, st>>>(d, ex->b);
+    ORBFE_CUDA(cudaGetLastError());
+    ex->bordersValid = 1;
     return 0;
 }
 

@@ -18,6 +18,7 @@ int orbfe_configure_kernels(int quadSmem, int fastSmem);
 int orbfe_blur_tiles(int w, int h);
 int orbfe_launch_extract(orbfe_extractor* ex, const uint8_t* d_images, int nframes, int lap0, int lap1, cudaStream_t st, int frame0);
 int orbfe_collect_stage_times(orbfe_extractor* ex);
+int orbfe_materialize_borders(orbfe_extractor* ex, cudaStream_t st);
 
 static thread_local char g_err[512] = "";
 
@@ -120,7 +121,7 @@ int orbfe_extractor_create(const orbfe_params* p, int device, int width, int hei
     ex->params = *p;
     ex->stream = nullptr; ex->copyIn = nullptr; ex->copyOut = nullptr;
     ex->hKps = nullptr; ex->hDesc = nullptr; ex->hCount = nullptr; ex->hMono = nullptr;
-    ex->profiling = 0; ex->stagePending = 0; ex->stereoPending = 0; ex->launches = 0;
+    ex->profiling = 0; ex->stagePending = 0; ex->stereoPending = 0; ex->launches = 0; ex->batchFrames = 0; ex->bordersValid = 0;
     memset(ex->ev, 0, sizeof ex->ev);
     memset(ex->stageMs, 0, sizeof ex->stageMs);
     memset(&ex->d, 0, sizeof ex->d);
@@ -260,7 +261,7 @@ int orbfe_extractor_create(const orbfe_params* p, int device, int width, int hei
             L.tabX = (int)tabs.size();
             linear_table(d.lv[l - 1].w, L.w, tabs);
             /* the last column group may be partial (w % 4 != 0): it runs through the same four-pixel path with the last
-               entry repeated; the 1-3 surplus bytes fall in the border, which k_pyramid_borders rewrites afterwards */
+               entry repeated; the 1-3 surplus bytes fall in the border, which k_pyramid_fringe rewrites afterwards */
             while ((tabs.size() - L.tabX) % 4) tabs.push_back(tabs.back());
             for (int x = 0; x + 3 < L.w; x += 4)
                 if (tabs[L.tabX + x + 3].x - tabs[L.tabX + x].x > 6) {
@@ -553,6 +554,11 @@ int orbfe_pyramid_level(orbfe_extractor* ex, int frame, int level, int padded, u
     if (!ex || !dst || level < 0 || level >= ex->d.nlevels || frame < 0 || frame >= ex->maxBatch) return ORBFE_E_INVALID;
     ORBFE_CUDA(cudaSetDevice(ex->device));
     ORBFE_CUDA(cudaDeviceSynchronize());
+    if (padded) {   /* the extraction writes only the 3 px of border it reads itself; the rest is filled here, once per batch */
+        int rc = orbfe_materialize_borders(ex, ex->stream);
+        if (rc) return rc;
+        ORBFE_CUDA(cudaStreamSynchronize(ex->stream));
+    }
     const LevelDesc& L = ex->d.lv[level];
     const int B = padded ? ORBFE_EDGE : 0;
     const uint8_t* src = ex->b.pyr + (size_t)frame * ex->d.pyrSlab + L.pyrOff + (size_t)(ORBFE_EDGE - B) * L.pitch + ORBFE_ROW_LEAD - B;

@@ -133,6 +133,8 @@ struct orbfe_extractor {
     double stageMs[ORBFE_NUM_STAGES + 2];
     int stagePending, stereoPending;
     long long launches;   /* kernels launched so far by this object */
+    int batchFrames;      /* frames of the last batch (chunks of the host pipeline accumulate) */
+    int bordersValid;     /* the 19 px pyramid border of those frames has been written (orbfe_materialize_borders) */
     /* pinned host staging for the host entry points */
     orbfe_keypoint* hKps;
     uint8_t* hDesc;
