@@ -571,7 +571,7 @@ __global__ void __launch_bounds__(FAST_NT, 8) k_fast_cells_list(const __grid_con
 /* One warp = one strip (120 columns x up to 48 rows) of one level of one frame; warps are independent (no block
  * barrier).  Each lane owns four adjacent columns.  Per row the warp loads the row three below (coalesced 128 B),
  * keeps the last 16 rows in a shared-memory ring, and runs the 4-pixel sieve on registers (left/right neighbours come
- * by shuffle).  Every FS_R rows the sieve's survivors are compacted (per-lane counts, one warp scan) into a queue,
+ * by shuffle).  Every FS_R rows the sieve's survivors are compacted (per-lane bit masks, one warp scan) into a queue,
  * the exact 9-of-16 test runs densely over the queue (corners compacted in place), scores are computed for the corners
  * and each corner (x, y, score) is appended to the raw list of the 35-px cell that contains it (one global atomic).
  * k_fast_nms then does the cell-local non-maximum suppression and ordering. */
@@ -579,7 +579,6 @@ __global__ void __launch_bounds__(FAST_NT, 8) k_fast_cells_list(const __grid_con
 #define FS_PW 33               /* words per buffered row: 32 + 1 so that equal columns of different rows hit different banks */
 __global__ void __launch_bounds__(FS_WARPS * 32, 8) k_fast_stream(const __grid_constant__ ExDesc d, ExBuffers b, int stripBase, int nStrips) {
     __shared__ __align__(16) uint32_t s_buf[FS_WARPS][FS_BROWS][FS_PW];
-    __shared__ uint32_t s_hits[FS_WARPS][FS_R][32];
     __shared__ uint16_t s_q[FS_WARPS][FS_R * FS_COLS + 32];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const size_t f = blockIdx.y;
@@ -611,7 +610,10 @@ __global__ void __launch_bounds__(FS_WARPS * 32, 8) k_fast_stream(const __grid_c
     for (int c0 = 0; c0 < nrows; c0 += FS_R) {
         const int rows = min(FS_R, nrows - c0);
         __syncwarp();
-        /* 1. sieve, one row per step: buffer rows r (y-3), r+3 (y), r+6 (y+3, fetched one step earlier) */
+        /* 1. sieve, one row per step: buffer rows r (y-3), r+3 (y), r+6 (y+3, fetched one step earlier).  The survivors of
+         *    my four columns collect in hm, one nibble per row: the high half of h * 0x02040810 holds bits 7, 15, 23, 31 of h
+         *    in its low nibble, and the funnel shift keeps exactly that nibble */
+        uint32_t hm = 0;
         for (int r = 0; r < rows; r++) {
             const uint32_t top = nxt;
             p += pitch;
@@ -619,23 +621,27 @@ __global__ void __launch_bounds__(FS_WARPS * 32, 8) k_fast_stream(const __grid_c
             buf[(r + 6) * FS_PW + lane] = top;
             const uint32_t cen = buf[(r + 3) * FS_PW + lane], bot = buf[r * FS_PW + lane];
             const uint32_t lw = __shfl_up_sync(0xFFFFFFFFu, cen, 1), rw = __shfl_down_sync(0xFFFFFFFFu, cen, 1);
-            s_hits[warp][r][lane] = fast_sieve4(cen, top, bot, __byte_perm(lw, cen, 0x4321), __byte_perm(cen, rw, 0x6543), k127mt) & vmask;
+            const uint32_t h = fast_sieve4(cen, top, bot, __byte_perm(lw, cen, 0x4321), __byte_perm(cen, rw, 0x6543), k127mt) & vmask;
+            hm = __funnelshift_r(hm, __umulhi(h, 0x02040810u), 4);
         }
+        hm >>= 4 * (FS_R - rows);   /* bit 4r + k: row r of the chunk, column k of my word */
         __syncwarp();
-        /* 2. compaction in (row, byte, lane) order: one ballot per byte position of each row gives every survivor its
-         *    queue slot; consecutive entries then sit in different columns, i.e. different shared-memory banks */
-        int n = 0;
-        const uint32_t ltmask = (1u << lane) - 1;
-        for (int r = 0; r < rows; r++) {
-            const uint32_t h = s_hits[warp][r][lane];
-            if (!__any_sync(0xFFFFFFFFu, h != 0)) continue;
-            const int ent = r * (4 * FS_PW) + 4 * lane;                          /* byte offset of my byte 0 from bufb */
+        /* 2. compaction: one warp scan of the per-lane counts gives every lane its run of queue slots */
+        const int cnt = __popc(hm);
+        int incl = cnt;
 #pragma unroll
-            for (int k = 0; k < 4; k++) {
-                const bool on = (h >> (8 * k + 7)) & 1u;
-                const uint32_t bal = __ballot_sync(0xFFFFFFFFu, on);
-                if (on) q[n + __popc(bal & ltmask)] = (uint16_t)(ent + k);
-                n += __popc(bal);
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+            if (lane >= o) incl += t;
+        }
+        const int n = __shfl_sync(0xFFFFFFFFu, incl, 31);
+        {
+            int pos = incl - cnt;
+            uint32_t m = hm;
+            while (m) {
+                const int bit = __ffs(m) - 1;
+                m &= m - 1;
+                q[pos++] = (uint16_t)((bit >> 2) * (4 * FS_PW) + 4 * lane + (bit & 3));   /* byte offset from bufb */
             }
         }
         if (n > 0) {

@@ -244,6 +244,55 @@ def test_stereo_batch_and_no_match_frame():
     exL.close(); exR.close()
 
 
+def test_kitti_full_size_batch_properties():
+    """BASELINE config 4 at full size: 4096 KITTI-shaped images (2048 stereo pairs, 1241x376, 2000 features) in one device
+    batch per camera.  The batch is 16 distinct pairs repeated in a scrambled order: every frame must give exactly what its
+    first occurrence gives (position independence across the whole batch), and the 16 distinct pairs must give the oracle's
+    keypoints, descriptors and stereo matches."""
+    import torch
+    W, H, params, mbf, fx = 1241, 376, (2000, 1.2, 8, 20, 7), 386.1448, 718.856
+    ND, NP = 16, 2048
+    pairs = [synth.stereo_pair(700 + i, W, H) for i in range(ND)]
+    order = (np.arange(NP) * 7 + (np.arange(NP) // ND) * 3) % ND            # every source appears 128 times, scattered
+    order[:ND] = np.arange(ND)                                             # ... and first in its natural position
+    st = torch.cuda.Stream()
+    with torch.cuda.stream(st):
+        dL = torch.from_numpy(np.stack([p[0] for p in pairs])).cuda()[torch.from_numpy(order).cuda()].contiguous()
+        dR = torch.from_numpy(np.stack([p[1] for p in pairs])).cuda()[torch.from_numpy(order).cuda()].contiguous()
+    st.synchronize()
+    exL = ORBextractor(*params, width=W, height=H, max_batch=NP)
+    exR = ORBextractor(*params, width=W, height=H, max_batch=NP)
+    exL.extract_batch_device(dL.data_ptr(), NP, (0, 0), st.cuda_stream)
+    exR.extract_batch_device(dR.data_ptr(), NP, (0, 0), st.cuda_stream)
+    M.compute_stereo_matches(exL, exR, NP, mbf, 0.0, fx, stream=st.cuda_stream)
+    st.synchronize()
+    cntL, monoL = exL.batch_counts(NP)
+    cntR, monoR = exR.batch_counts(NP)
+    assert np.array_equal(cntL, cntL[order]) and np.array_equal(cntR, cntR[order]) and np.array_equal(monoL, cntL)
+    assert cntL.min() > 1500
+    first = {}
+    for f in range(NP):
+        _, k, d = exL.batch_result(f)
+        _, kr, dr = exR.batch_result(f)
+        u, dep = M.stereo_result(exL, f)
+        s = int(order[f])
+        if f < ND:
+            first[s] = (k, d, kr, dr, u, dep)
+        else:
+            w = first[s]
+            assert np.array_equal(k, w[0]) and np.array_equal(d, w[1]) and np.array_equal(kr, w[2]) and np.array_equal(dr, w[3]), "frame %d" % f
+            assert np.array_equal(u, w[4]) and np.array_equal(dep, w[5]), "stereo of frame %d" % f
+    oL, oR = O.OracleExtractor(*params), O.OracleExtractor(*params)
+    for s_ in range(ND):
+        _, okL, odL = oL(pairs[s_][0]); _, okR, odR = oR(pairs[s_][1])
+        kept, ou, od = O.stereo_match(oL, oR, okL, odL, okR, odR, mbf, 0.0, fx)
+        k, d, kr, dr, u, dep = first[s_]
+        assert_same_keypoints(k, okL, "pair %d left" % s_); assert_same_keypoints(kr, okR, "pair %d right" % s_)
+        assert np.array_equal(d, odL) and np.array_equal(dr, odR)
+        assert kept > 100 and np.array_equal(u, ou) and np.array_equal(dep, od), "pair %d stereo" % s_
+    exL.close(); exR.close()
+
+
 def test_descriptor_distance_known_answers():
     z = np.zeros(32, np.uint8); o = np.full(32, 255, np.uint8)
     one = z.copy(); one[9] = 0x40
