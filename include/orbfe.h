@@ -183,6 +183,16 @@ int orbfe_hamming_top2(int device, const uint8_t* q, int nq, const uint8_t* db, 
 int orbfe_knn2_ratio(int device, const uint8_t* q, int nq, const uint8_t* t, int nt, double ratio, int32_t* match,
                      int32_t* d0, int32_t* d1);
 
+/* Replaces the computation of MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:349-423) for many map points at once
+ * (SURVEY.md §8f N4): map point p owns the descriptor rows [offsets[p], offsets[p+1]) (the rows of vDescriptors, :352-384);
+ * best_idx[p] = BestIdx, the row (relative to offsets[p]) with the least median distance to all rows of the point,
+ * median = sorted distances[int(0.5*(N-1))], first row on ties (:404-417); -1 for a point without rows.  best_median (may be
+ * NULL) receives BestMedian.  At most 65535 rows per point. */
+int orbfe_distinctive_descriptors_device(int device, const uint8_t* d_desc, const int32_t* d_offsets, int npoints, int32_t* d_best_idx,
+                                         int32_t* d_best_median, void* stream);
+int orbfe_distinctive_descriptors(int device, const uint8_t* desc, const int32_t* offsets, int npoints, int32_t* best_idx,
+                                  int32_t* best_median);
+
 /* ------------------------------------------------------------------------------- projection-gated search (N1) */
 /* Replaces the search of Tracking::SearchLocalPoints (src/Tracking.cc:3430-3524):
  *   int ORBmatcher::SearchByProjection(Frame &F, const vector<MapPoint*> &vpMapPoints, const float th, const bool bFarPoints,

@@ -203,4 +203,33 @@ void orc_knn2_ratio(const uint8_t* q, int nq, const uint8_t* t, int nt, double r
     }
 }
 
+/* MapPoint::ComputeDistinctiveDescriptors, src/MapPoint.cc:386-417, for npoints map points (rows offsets[p]..offsets[p+1]). */
+void orc_distinctive_descriptors(const uint8_t* desc, const int32_t* offsets, int npoints, int32_t* best_idx, int32_t* best_median) {
+    for (int p = 0; p < npoints; p++) {
+        const uint8_t* d = desc + (size_t)offsets[p] * 32;
+        const size_t N = (size_t)(offsets[p + 1] - offsets[p]);
+        best_idx[p] = -1;
+        if (best_median) best_median[p] = INT_MAX;
+        if (N == 0) continue;
+        std::vector<float> Distances(N * N);
+        for (size_t i = 0; i < N; i++) {
+            Distances[i * N + i] = 0;
+            for (size_t j = i + 1; j < N; j++) {
+                const int distij = descriptor_distance(d + i * 32, d + j * 32);
+                Distances[i * N + j] = distij;
+                Distances[j * N + i] = distij;
+            }
+        }
+        int BestMedian = INT_MAX, BestIdx = 0;
+        for (size_t i = 0; i < N; i++) {
+            std::vector<int> vDists(Distances.begin() + i * N, Distances.begin() + (i + 1) * N);
+            std::sort(vDists.begin(), vDists.end());
+            const int median = vDists[0.5 * (N - 1)];
+            if (median < BestMedian) { BestMedian = median; BestIdx = (int)i; }
+        }
+        best_idx[p] = BestIdx;
+        if (best_median) best_median[p] = BestMedian;
+    }
+}
+
 }  /* extern "C" */

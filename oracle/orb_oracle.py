@@ -62,6 +62,7 @@ def lib():
     L.orc_knn2_ratio.argtypes = [vp, C.c_int, vp, C.c_int, C.c_double, vp, vp, vp]
     L.orc_remap_linear_u8.argtypes = [vp, C.c_int, C.c_int, C.c_int, vp, vp, vp, C.c_int]
     L.orc_to_gray.argtypes = [vp, C.c_longlong, C.c_int, C.c_int, vp]
+    L.orc_distinctive_descriptors.argtypes = [vp, vp, C.c_int, vp, vp]
     L.orc_search_by_projection.argtypes = [vp, vp, C.c_int, C.c_int, vp, vp, vp, vp, vp, vp, C.c_int, C.c_int, C.c_float, vp]
     L.orc_search_by_projection.restype = C.c_int
     L.orc_clahe_u8.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_double, C.c_int, C.c_int, vp, C.c_int, vp]
@@ -218,6 +219,16 @@ def to_gray(img, rgb):
     dst = np.zeros(img.shape[:2], np.uint8)
     lib().orc_to_gray(_ptr(img), img.shape[0] * img.shape[1], img.shape[2], int(rgb), _ptr(dst))
     return dst
+
+
+def distinctive_descriptors(desc, offsets):
+    """MapPoint::ComputeDistinctiveDescriptors for many map points; returns (BestIdx, BestMedian) per point."""
+    desc = np.ascontiguousarray(desc, np.uint8)
+    off = np.ascontiguousarray(offsets, np.int32)
+    idx = np.zeros(off.shape[0] - 1, np.int32)
+    med = np.zeros(off.shape[0] - 1, np.int32)
+    lib().orc_distinctive_descriptors(_ptr(desc), _ptr(off), off.shape[0] - 1, _ptr(idx), _ptr(med))
+    return idx, med
 
 
 PROJ_QUERY_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("radius", "<f4"), ("xr", "<f4"), ("min_level", "<i4"), ("max_level", "<i4"),

@@ -71,6 +71,8 @@ SIGNATURES = {
     "orbfe_rectify_batch_device": (i32, [vp, vp, vp, i32, vp]),
     "orbfe_rectify": (i32, [vp, vp, sz, vp, sz]),
     "orbfe_to_gray_device": (i32, [i32, vp, i32, i32, i32, i32, i32, vp, vp]),
+    "orbfe_distinctive_descriptors_device": (i32, [i32, vp, vp, i32, vp, vp, vp]),
+    "orbfe_distinctive_descriptors": (i32, [i32, vp, vp, i32, vp, vp]),
     "orbfe_search_by_projection_device": (i32, [i32, i32, i32, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, C.c_float, vp, vp, vp]),
     "orbfe_search_by_projection": (i32, [i32, vp, vp, i32, i32, vp, vp, vp, vp, vp, vp, i32, i32, C.c_float, vp, C.POINTER(i32)]),
     "orbfe_clahe_create": (i32, [i32, i32, i32, C.c_double, i32, i32, i32, C.POINTER(vp)]),

@@ -8,6 +8,7 @@
  * The Hamming work is XOR + POPC on the integer pipe (8 x 32-bit per 256-bit pair); it is deliberately not
  * reshaped into a tensor-core contraction (BASELINE.json north_star). */
 #include <cuda_runtime.h>
+#include <limits.h>
 #include <stdint.h>
 #include <string.h>
 
@@ -383,6 +384,41 @@ static bool same_geometry(const orbfe_extractor* a, const orbfe_extractor* b) {
            a->d.kpCap == b->d.kpCap && a->d.pyrSlab == b->d.pyrSlab && a->params.scale_factor == b->params.scale_factor;
 }
 
+/* MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:349-423) for many map points at once: point p owns the descriptor
+ * rows [off[p], off[p+1]) (its observations); the representative is the row with the least median distance to all rows of
+ * the point (its own 0 included), median = sorted[int(0.5*(N-1))], first row on ties.  One warp = one map point, one lane =
+ * one row at a time.  The median of a row is the smallest v with #(d <= v) > rank, found by bisection on v in [0, 256]: nine
+ * passes over the point's rows, no sort, no N x N matrix. */
+#define DD_WARPS 4
+__global__ void __launch_bounds__(DD_WARPS * 32) k_distinctive(const uint4* __restrict__ desc, const int* __restrict__ off, int npoints,
+                                                               int* __restrict__ bestIdx, int* __restrict__ bestMedian) {
+    const int p = blockIdx.x * DD_WARPS + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (p >= npoints) return;
+    const int r0 = off[p], n = off[p + 1] - r0;
+    if (n <= 0) {
+        if (lane == 0) { bestIdx[p] = -1; if (bestMedian) bestMedian[p] = INT_MAX; }
+        return;
+    }
+    const int rank = (int)(0.5 * (n - 1));
+    const uint4* d = desc + (size_t)r0 * 2;
+    unsigned best = 0xFFFFFFFFu;   /* median << 16 | row */
+    for (int i = lane; i < n; i += 32) {
+        uint32_t q[8];
+        { const uint4 a = __ldg(d + 2 * i), b = __ldg(d + 2 * i + 1); q[0] = a.x; q[1] = a.y; q[2] = a.z; q[3] = a.w; q[4] = b.x; q[5] = b.y; q[6] = b.z; q[7] = b.w; }
+        int lo = 0, hi = 256;      /* the median lies in [lo, hi] */
+        while (lo < hi) {
+            const int mid = (lo + hi) >> 1;
+            int cnt = 0;
+            for (int j = 0; j < n; j++) cnt += ham256(q, __ldg(d + 2 * j), __ldg(d + 2 * j + 1)) <= mid ? 1 : 0;
+            if (cnt > rank) hi = mid; else lo = mid + 1;
+        }
+        best = min(best, ((unsigned)lo << 16) | (unsigned)min(i, 0xFFFF));
+    }
+#pragma unroll
+    for (int o = 16; o; o >>= 1) best = min(best, __shfl_xor_sync(0xFFFFFFFFu, best, o));
+    if (lane == 0) { bestIdx[p] = (int)(best & 0xFFFFu); if (bestMedian) bestMedian[p] = (int)(best >> 16); }
+}
+
 extern "C" {
 
 int orbfe_stereo_match_batch_device(orbfe_extractor* exL, orbfe_extractor* exR, int nframes, float mbf, float minD, float maxD, void* stream) {
@@ -580,6 +616,42 @@ int orbfe_descriptor_distances(int device, const uint8_t* a, const uint8_t* b, i
     if (e == cudaSuccess) e = cudaMemcpy(out, dout, (size_t)n * 4, cudaMemcpyDeviceToHost);
     cudaFree(da); cudaFree(db); cudaFree(dout);
     if (e != cudaSuccess) return orbfe_cuda_fail(e, "descriptor_distances");
+    return ORBFE_OK;
+}
+
+int orbfe_distinctive_descriptors_device(int device, const uint8_t* d_desc, const int32_t* d_offsets, int npoints, int32_t* d_best_idx,
+                                         int32_t* d_best_median, void* stream) {
+    if (!d_desc || !d_offsets || !d_best_idx || npoints < 1) { orbfe_set_error("bad argument"); return ORBFE_E_INVALID; }
+    if ((uintptr_t)d_desc & 15) { orbfe_set_error("descriptor array must be 16-byte aligned"); return ORBFE_E_INVALID; }
+    ORBFE_CUDA(cudaSetDevice(device));
+    k_distinctive<<<(npoints + DD_WARPS - 1) / DD_WARPS, DD_WARPS * 32, 0, (cudaStream_t)stream>>>((const uint4*)d_desc, d_offsets, npoints, d_best_idx, d_best_median);
+    ORBFE_CUDA(cudaGetLastError());
+    return ORBFE_OK;
+}
+
+int orbfe_distinctive_descriptors(int device, const uint8_t* desc, const int32_t* offsets, int npoints, int32_t* best_idx, int32_t* best_median) {
+    if (!desc || !offsets || !best_idx || npoints < 1) { orbfe_set_error("bad argument"); return ORBFE_E_INVALID; }
+    for (int p = 0; p < npoints; p++)
+        if (offsets[p + 1] < offsets[p] || offsets[p + 1] - offsets[p] > 65535) { orbfe_set_error("map point %d: bad row range (at most 65535 observations)", p); return ORBFE_E_INVALID; }
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev) {
+        orbfe_set_error("no usable CUDA device %d (found %d); this library has no CPU path", device, ndev);
+        return ORBFE_E_CUDA;
+    }
+    ORBFE_CUDA(cudaSetDevice(device));
+    const size_t rows = (size_t)offsets[npoints], bDesc = (rows * 32 + 255) & ~(size_t)255, bOff = ((size_t)(npoints + 1) * 4 + 255) & ~(size_t)255;
+    const size_t bOut = ((size_t)npoints * 4 + 255) & ~(size_t)255;
+    uint8_t* d = nullptr;
+    ORBFE_CUDA(cudaMalloc((void**)&d, bDesc + bOff + 2 * bOut + 256));
+    cudaError_t e = rows ? cudaMemcpy(d, desc, rows * 32, cudaMemcpyHostToDevice) : cudaSuccess;
+    if (e == cudaSuccess) e = cudaMemcpy(d + bDesc, offsets, (size_t)(npoints + 1) * 4, cudaMemcpyHostToDevice);
+    int rc = ORBFE_OK;
+    if (e == cudaSuccess) rc = orbfe_distinctive_descriptors_device(device, d, (const int32_t*)(d + bDesc), npoints, (int32_t*)(d + bDesc + bOff), (int32_t*)(d + bDesc + bOff + bOut), nullptr);
+    if (rc == ORBFE_OK && e == cudaSuccess) e = cudaMemcpy(best_idx, d + bDesc + bOff, (size_t)npoints * 4, cudaMemcpyDeviceToHost);
+    if (rc == ORBFE_OK && e == cudaSuccess && best_median) e = cudaMemcpy(best_median, d + bDesc + bOff + bOut, (size_t)npoints * 4, cudaMemcpyDeviceToHost);
+    cudaFree(d);
+    if (rc != ORBFE_OK) return rc;
+    if (e != cudaSuccess) return orbfe_cuda_fail(e, "distinctive_descriptors");
     return ORBFE_OK;
 }
 

@@ -105,3 +105,15 @@ def knn2_ratio(queries, train, ratio=0.7, device=0):
     m = np.zeros(q.shape[0], np.int32); d0 = m.copy(); d1 = m.copy()
     check(_lib.lib().orbfe_knn2_ratio(device, ptr(q), q.shape[0], ptr(t), t.shape[0], float(ratio), ptr(m), ptr(d0), ptr(d1)))
     return m, d0, d1
+
+
+def distinctive_descriptors(desc, offsets, device=0):
+    """MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:349-423) for many map points: point p owns rows
+    offsets[p]:offsets[p+1] of desc.  Returns (best_idx, best_median) per point (best_idx relative to the point's first row)."""
+    desc = np.ascontiguousarray(desc, np.uint8)
+    off = np.ascontiguousarray(offsets, np.int32)
+    npts = off.shape[0] - 1
+    idx = np.zeros(npts, np.int32)
+    med = np.zeros(npts, np.int32)
+    check(_lib.lib().orbfe_distinctive_descriptors(device, ptr(desc), ptr(off), npts, ptr(idx), ptr(med)))
+    return idx, med
