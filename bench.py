@@ -447,6 +447,40 @@ def main():
                   "ms_per_step": pj_ms, "frames_per_step": PF * world, "keypoints_per_frame": 1200, "map_points_per_frame": int(pj_qoff[1]),
                   "accepted_per_step": pj_acc, "note": "ORBmatcher::SearchByProjection(Frame&, vpMapPoints, th=1) incl. the frame grid; device resident"}
 
+    # ---- bag-of-words assignment: Frame::ComputeBoW on the left frames the extractor just produced (device
+    #      buffers chained), ORBvoc-shaped synthetic vocabulary (k = 10, L = 6, 1.1 M nodes, TF-IDF, L1)
+    from orb_slam3_detailed_comments_kor_b200.bow import ORBVocabulary
+    vrng = np.random.RandomState(77)
+    v_parent, v_desc = [], []
+    level_ids, level_desc, next_id = np.array([0]), vrng.randint(0, 256, (1, 32)).astype(np.uint8), 1
+    for lvl in range(1, 7):
+        nch = len(level_ids) * 10
+        flip = vrng.randint(0, 256, (nch, 32)).astype(np.uint8) & vrng.randint(0, 256, (nch, 32)).astype(np.uint8)
+        for _ in range(lvl):
+            flip &= vrng.randint(0, 256, (nch, 32)).astype(np.uint8)                  # fewer flipped bits further down the tree
+        d = np.repeat(level_desc, 10, axis=0) ^ flip
+        v_parent.append(np.repeat(level_ids, 10)); v_desc.append(d)
+        level_ids, level_desc, next_id = np.arange(next_id, next_id + nch), d, next_id + nch
+    v_parent = np.concatenate(v_parent).astype(np.int32); v_desc = np.concatenate(v_desc)
+    v_leaf = np.zeros(len(v_parent), np.uint8); v_leaf[-1000000:] = 1
+    v_weight = np.where(v_leaf == 1, vrng.uniform(0.5, 9.0, len(v_parent)), 0.0)
+    voc = ORBVocabulary(10, 6, 0, 0, v_parent, v_leaf, v_desc, v_weight, max_features=exL.capacity, max_batch=P, device=local_rank)
+    vk, vd, vc, vm = C.c_void_p(), C.c_void_p(), C.c_void_p(), C.c_void_p()
+    _lib.check(L.orbfe_batch_device_views(exL.handle, C.byref(vk), C.byref(vd), C.byref(vc), C.byref(vm)))
+    for _ in range(3):
+        voc.transform_batch_device(vd.value, exL.capacity, vc.value, P, 4, stream=st)
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        voc.transform_batch_device(vd.value, exL.capacity, vc.value, P, 4, stream=st)
+    e1.record()
+    barrier()
+    bow_ms = max_over_ranks(e0.elapsed_time(e1) / args.steps)
+    bow = {"value": P * world / (bow_ms / 1e3), "unit": "frames/s", "ms_per_step": bow_ms, "frames_per_step": P * world,
+           "features_per_frame": nkp, "vocabulary": "synthetic k=10 L=6 (1111110 nodes, 10^6 words), TF-IDF, L1",
+           "words_in_frame0": int(len(voc.result(0, int(exL.batch_counts(1)[0][0]))["bow_words"])),
+           "note": "Frame::ComputeBoW = DBoW2 transform(features, BowVec, FeatVec, 4); extractor buffers chained on the device"}
+
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cores = os.cpu_count() or 1
@@ -467,6 +501,14 @@ def main():
         with ThreadPoolExecutor(cores) as tp:
             list(tp.map(pj_cpu, range(reps)))
         pdt = time.perf_counter() - t0
+        ovoc = O.OracleVocabulary(10, 6, 0, 0, v_parent, v_leaf, v_desc, v_weight)
+        cntL0, _, _, descL0 = exL.extract_batch_host(hLn[:8], (0, 0))
+        bsample = [np.ascontiguousarray(descL0[i, :cntL0[i]]) for i in range(8)]
+        t0 = time.perf_counter()
+        with ThreadPoolExecutor(cores) as tp:
+            list(tp.map(lambda i: ovoc.transform(bsample[i % 8], 4), range(8 * cores)))
+        bdt = time.perf_counter() - t0
+        cpu["bow"] = {"value": 8 * cores / bdt, "unit": "frames/s", "sample": "%d frames (%.2f s wall) frame-parallel over %d threads" % (8 * cores, bdt, cores)}
         cpu["projection"] = {"value": reps * int(pj_qoff[1]) / pdt, "unit": "map_point_searches/s",
                              "sample": "%d frames (%.2f s wall) frame-parallel over %d threads" % (reps, pdt, cores)}
 
@@ -478,7 +520,7 @@ def main():
                            "l2": "inputs_larger_than_L2 (%d MB of images per step per GPU)" % (2 * P * W * H >> 20),
                            "mean_keypoints_per_frame": nkp, "parallelism": "frames sharded by rank, no collective"},
                 "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
-                "single_frame_latency_ms": single_ms, "rectify": rectify, "projection": projection,
+                "single_frame_latency_ms": single_ms, "rectify": rectify, "projection": projection, "bow": bow,
                 "gpu_launches": (2 * (PARAMS[2] + 8) + 3) * args.steps,
                 "hamming": hamming}
         print(json.dumps(line), flush=True)

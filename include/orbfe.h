@@ -183,6 +183,40 @@ int orbfe_hamming_top2(int device, const uint8_t* q, int nq, const uint8_t* db, 
 int orbfe_knn2_ratio(int device, const uint8_t* q, int nq, const uint8_t* t, int nt, double ratio, int32_t* match,
                      int32_t* d0, int32_t* d1);
 
+/* ------------------------------------------------------------------------------------ bag-of-words assignment (N2) */
+/* Replaces Frame::ComputeBoW / KeyFrame::ComputeBoW (src/Frame.cc:724-731, src/KeyFrame.cc:105-114):
+ *   mpORBvocabulary->transform(vCurrentDesc, mBowVec, mFeatVec, 4)
+ * i.e. DBoW2's TemplatedVocabulary<FORB::TDescriptor, FORB>::transform(features, BowVector&, FeatureVector&, levelsup)
+ * (Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1125-1193) with the per-feature tree descent of :1217-1260.
+ * The vocabulary is handed over as the rows of the text file that ORBVocabulary::loadFromTextFile reads (:1338-1426), in file
+ * order: row r is node r+1 (node 0 is the root); parent[r], is_leaf[r], 32 descriptor bytes, weight[r]; words are numbered in
+ * the order their rows appear.  k, L, scoring (ScoringType 0..5), weighting (WeightingType 0..3) are the four numbers of the
+ * file's first line.  max_features (<= 4096) / max_batch size the result buffers. */
+typedef struct orbfe_vocabulary orbfe_vocabulary;
+int orbfe_vocabulary_create(int device, int k, int L, int scoring, int weighting, int nrows, const int32_t* parent, const uint8_t* is_leaf,
+                            const uint8_t* desc, const double* weight, int max_features, int max_batch, orbfe_vocabulary** out);
+void orbfe_vocabulary_destroy(orbfe_vocabulary* v);
+int orbfe_vocabulary_words(const orbfe_vocabulary* v);
+/* A batch of frames on the device: frame f owns d_counts[f] descriptors at d_desc + (f*row_stride + i)*32 — the layout of
+ * orbfe_batch_device_views (row_stride = keypoint capacity), so the extractor's buffers can be passed as they are.
+ * Asynchronous on `stream` (NULL = the object's stream); results stay in the object until the next call. */
+int orbfe_bow_transform_batch_device(orbfe_vocabulary* v, const uint8_t* d_desc, int row_stride, const int32_t* d_counts, int nframes,
+                                     int levelsup, void* stream);
+/* Results of frame `frame` of the last batch, to the host (any pointer may be NULL):
+ *   word_ids / node_ids [nfeatures]: per feature the WordId and the NodeId at level L - levelsup (0 when that level is not
+ *     reached; the reference leaves *nid unset then);
+ *   bow_words / bow_values [*nbow]: mBowVec in key order (features whose word weight is 0 are left out, :1157);
+ *   fv_nodes [*nfv], fv_starts [*nfv + 1], fv_feats: mFeatVec in key order, node e owns fv_feats[fv_starts[e] .. fv_starts[e+1]). */
+int orbfe_bow_result(orbfe_vocabulary* v, int frame, int nfeatures, int32_t* word_ids, int32_t* node_ids, int32_t* bow_words, double* bow_values,
+                     int32_t* nbow, int32_t* fv_nodes, int32_t* fv_starts, int32_t* fv_feats, int32_t* nfv);
+/* One frame over host memory (copies inside, synchronous). */
+int orbfe_bow_transform(orbfe_vocabulary* v, const uint8_t* desc, int n, int levelsup, int32_t* word_ids, int32_t* node_ids, int32_t* bow_words,
+                        double* bow_values, int32_t* nbow, int32_t* fv_nodes, int32_t* fv_starts, int32_t* fv_feats, int32_t* nfv);
+/* Device views of the last batch (frame stride max_features; fv_starts: max_features + 1), for callers that keep going on the GPU. */
+int orbfe_bow_device_views(orbfe_vocabulary* v, const int32_t** d_feat_word, const int32_t** d_feat_node, const int32_t** d_bow_words,
+                           const double** d_bow_values, const int32_t** d_bow_count, const int32_t** d_fv_nodes, const int32_t** d_fv_starts,
+                           const int32_t** d_fv_feats, const int32_t** d_fv_count);
+
 /* Replaces the computation of MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:349-423) for many map points at once
  * (SURVEY.md §8f N4): map point p owns the descriptor rows [offsets[p], offsets[p+1]) (the rows of vDescriptors, :352-384);
  * best_idx[p] = BestIdx, the row (relative to offsets[p]) with the least median distance to all rows of the point,

@@ -1,0 +1,125 @@
+/* bow_oracle.cpp — CPU ORACLE (test infrastructure only; see orb_oracle.h for the rules).
+ * Bag-of-words assignment of Frame::ComputeBoW, restating
+ *   /root/reference/src/Frame.cc:724-731                                     mpORBvocabulary->transform(vCurrentDesc, mBowVec, mFeatVec, 4)
+ *   /root/reference/Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1125-1193   transform(features, BowVector&, FeatureVector&, levelsup)
+ *   /root/reference/Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1217-1260   transform(feature, word_id, weight, nid, levelsup)
+ *   /root/reference/Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1338-1426   loadFromTextFile (node / word numbering)
+ *   /root/reference/Thirdparty/DBoW2/DBoW2/BowVector.cpp:34-84, FeatureVector.cpp:31-45, FORB.cpp:81-101, ScoringObject.h:73-90
+ * The vocabulary file (Vocabulary/ORBvoc.txt) is not in /root/reference, so the tests run on synthetic trees; parity unpinned
+ * beyond the independent Python restatement in tests/test_bow.py. */
+#include <cmath>
+#include <cstdint>
+#include <cstring>
+#include <map>
+#include <vector>
+
+#include "orb_oracle.h"
+
+namespace {
+struct Node {
+    std::vector<int> children;
+    uint8_t descriptor[32];
+    double weight = 0;
+    int word_id = 0;
+    bool isLeaf() const { return children.empty(); }
+};
+}  // namespace
+
+struct orc_vocabulary {
+    int k, L, scoring, weighting, nwords;
+    std::vector<Node> nodes;
+};
+
+extern "C" {
+
+/* Rows as in the text file: node id = row + 1 (the root is node 0), `parent`, `is_leaf`, 32 descriptor bytes, weight; words
+ * are numbered in the order their rows appear. */
+orc_vocabulary* orc_vocabulary_create(int k, int L, int scoring, int weighting, int nrows, const int32_t* parent, const uint8_t* is_leaf,
+                                      const uint8_t* desc, const double* weight) {
+    orc_vocabulary* v = new orc_vocabulary();
+    v->k = k; v->L = L; v->scoring = scoring; v->weighting = weighting; v->nwords = 0;
+    v->nodes.resize(1);
+    for (int r = 0; r < nrows; r++) {
+        const int nid = (int)v->nodes.size();
+        v->nodes.resize(nid + 1);
+        if (parent[r] < 0 || parent[r] >= nid) { delete v; return nullptr; }
+        v->nodes[parent[r]].children.push_back(nid);
+        memcpy(v->nodes[nid].descriptor, desc + (size_t)r * 32, 32);
+        v->nodes[nid].weight = weight[r];
+        if (is_leaf[r]) v->nodes[nid].word_id = v->nwords++;
+    }
+    return v;
+}
+
+void orc_vocabulary_destroy(orc_vocabulary* v) { delete v; }
+int orc_vocabulary_words(const orc_vocabulary* v) { return v->nwords; }
+
+/* word_ids / node_ids / weights: per feature (also for stopped words); bow_*: the BowVector in key order; fv_*: the FeatureVector
+ * in key order, node e owns fv_feats[fv_starts[e] .. fv_starts[e+1]). */
+int orc_bow_transform(const orc_vocabulary* voc, const uint8_t* features, int n, int levelsup, int32_t* word_ids, int32_t* node_ids,
+                      int32_t* bow_words, double* bow_values, int32_t* nbow, int32_t* fv_nodes, int32_t* fv_starts, int32_t* fv_feats,
+                      int32_t* nfv) {
+    std::map<unsigned, double> v;
+    std::map<unsigned, std::vector<unsigned>> fv;
+    *nbow = 0; *nfv = 0;
+    if (voc->nodes.size() <= 1) return 0;   /* empty() */
+    const bool must = voc->scoring != 5;    /* DotProductScoring is the only one that does not normalise */
+    const bool l2 = voc->scoring == 1;
+    for (int i = 0; i < n; i++) {
+        const uint8_t* f = features + (size_t)i * 32;
+        /* transform(feature, word_id, weight, nid, levelsup) */
+        const int nid_level = voc->L - levelsup;
+        unsigned nid = 0;
+        int final_id = 0, current_level = 0;
+        do {
+            ++current_level;
+            const std::vector<int>& nodes = voc->nodes[final_id].children;
+            final_id = nodes[0];
+            double best_d = orc_descriptor_distance(f, voc->nodes[final_id].descriptor);
+            for (size_t c = 1; c < nodes.size(); c++) {
+                const double d = orc_descriptor_distance(f, voc->nodes[nodes[c]].descriptor);
+                if (d < best_d) { best_d = d; final_id = nodes[c]; }
+            }
+            if (current_level == nid_level) nid = final_id;
+        } while (!voc->nodes[final_id].isLeaf());
+        const unsigned id = voc->nodes[final_id].word_id;
+        const double w = voc->nodes[final_id].weight;
+        if (word_ids) word_ids[i] = (int32_t)id;
+        if (node_ids) node_ids[i] = (int32_t)nid;
+        if (w > 0) {
+            if (voc->weighting == 0 || voc->weighting == 1) {   /* TF_IDF, TF: addWeight */
+                auto it = v.lower_bound(id);
+                if (it != v.end() && it->first == id) it->second += w;
+                else v.insert(it, std::make_pair(id, w));
+            } else {                                            /* IDF, BINARY: addIfNotExist */
+                if (v.find(id) == v.end()) v[id] = w;
+            }
+            fv[nid].push_back((unsigned)i);
+        }
+    }
+    if ((voc->weighting == 0 || voc->weighting == 1) && !v.empty() && !must) {
+        const double nd = (double)v.size();
+        for (auto& e : v) e.second /= nd;
+    }
+    if (must) {
+        double norm = 0.0;
+        if (!l2) { for (auto& e : v) norm += std::fabs(e.second); }
+        else { for (auto& e : v) norm += e.second * e.second; norm = std::sqrt(norm); }
+        if (norm > 0.0) for (auto& e : v) e.second /= norm;
+    }
+    int k = 0;
+    for (auto& e : v) { bow_words[k] = (int32_t)e.first; bow_values[k] = e.second; k++; }
+    *nbow = k;
+    int e = 0, pos = 0;
+    for (auto& nd : fv) {
+        fv_nodes[e] = (int32_t)nd.first;
+        fv_starts[e] = pos;
+        for (unsigned i : nd.second) fv_feats[pos++] = (int32_t)i;
+        e++;
+    }
+    fv_starts[e] = pos;
+    *nfv = e;
+    return 0;
+}
+
+}  /* extern "C" */

@@ -62,6 +62,11 @@ def lib():
     L.orc_knn2_ratio.argtypes = [vp, C.c_int, vp, C.c_int, C.c_double, vp, vp, vp]
     L.orc_remap_linear_u8.argtypes = [vp, C.c_int, C.c_int, C.c_int, vp, vp, vp, C.c_int]
     L.orc_to_gray.argtypes = [vp, C.c_longlong, C.c_int, C.c_int, vp]
+    L.orc_vocabulary_create.restype = vp
+    L.orc_vocabulary_create.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp, vp, vp, vp]
+    L.orc_vocabulary_destroy.argtypes = [vp]
+    L.orc_vocabulary_words.argtypes = [vp]
+    L.orc_bow_transform.argtypes = [vp, vp, C.c_int, C.c_int, vp, vp, vp, vp, vp, vp, vp, vp, vp]
     L.orc_distinctive_descriptors.argtypes = [vp, vp, C.c_int, vp, vp]
     L.orc_search_by_projection.argtypes = [vp, vp, C.c_int, C.c_int, vp, vp, vp, vp, vp, vp, C.c_int, C.c_int, C.c_float, vp]
     L.orc_search_by_projection.restype = C.c_int
@@ -219,6 +224,39 @@ def to_gray(img, rgb):
     dst = np.zeros(img.shape[:2], np.uint8)
     lib().orc_to_gray(_ptr(img), img.shape[0] * img.shape[1], img.shape[2], int(rgb), _ptr(dst))
     return dst
+
+
+class OracleVocabulary:
+    """DBoW2 TemplatedVocabulary<FORB> built from text-file rows; transform() = Frame::ComputeBoW's call."""
+
+    def __init__(self, k, L, scoring, weighting, parent, is_leaf, desc, weight):
+        parent = np.ascontiguousarray(parent, np.int32); is_leaf = np.ascontiguousarray(is_leaf, np.uint8)
+        desc = np.ascontiguousarray(desc, np.uint8); weight = np.ascontiguousarray(weight, np.float64)
+        self.L = lib()
+        self.h = self.L.orc_vocabulary_create(k, L, scoring, weighting, parent.shape[0], _ptr(parent), _ptr(is_leaf), _ptr(desc), _ptr(weight))
+        if not self.h:
+            raise ValueError("bad vocabulary rows")
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.L.orc_vocabulary_destroy(self.h)
+            self.h = None
+
+    def words(self):
+        return self.L.orc_vocabulary_words(self.h)
+
+    def transform(self, desc, levelsup=4):
+        desc = np.ascontiguousarray(desc, np.uint8)
+        n = desc.shape[0]
+        wid, nid = np.zeros(n, np.int32), np.zeros(n, np.int32)
+        bw, bv = np.zeros(max(n, 1), np.int32), np.zeros(max(n, 1), np.float64)
+        fn, fs, ff = np.zeros(max(n, 1), np.int32), np.zeros(n + 1, np.int32), np.zeros(max(n, 1), np.int32)
+        nb, nf = C.c_int(0), C.c_int(0)
+        self.L.orc_bow_transform(self.h, _ptr(desc), n, levelsup, _ptr(wid), _ptr(nid), _ptr(bw), _ptr(bv), C.byref(nb), _ptr(fn), _ptr(fs), _ptr(ff),
+                                 C.byref(nf))
+        nb, nf = nb.value, nf.value
+        return {"word_ids": wid, "node_ids": nid, "bow_words": bw[:nb].copy(), "bow_values": bv[:nb].copy(),
+                "feat_vec": {int(fn[e]): ff[fs[e]:fs[e + 1]].copy() for e in range(nf)}}
 
 
 def distinctive_descriptors(desc, offsets):

@@ -71,6 +71,13 @@ SIGNATURES = {
     "orbfe_rectify_batch_device": (i32, [vp, vp, vp, i32, vp]),
     "orbfe_rectify": (i32, [vp, vp, sz, vp, sz]),
     "orbfe_to_gray_device": (i32, [i32, vp, i32, i32, i32, i32, i32, vp, vp]),
+    "orbfe_vocabulary_create": (i32, [i32, i32, i32, i32, i32, i32, vp, vp, vp, vp, i32, i32, C.POINTER(vp)]),
+    "orbfe_vocabulary_destroy": (None, [vp]),
+    "orbfe_vocabulary_words": (i32, [vp]),
+    "orbfe_bow_transform_batch_device": (i32, [vp, vp, i32, vp, i32, i32, vp]),
+    "orbfe_bow_result": (i32, [vp, i32, i32, vp, vp, vp, vp, C.POINTER(i32), vp, vp, vp, C.POINTER(i32)]),
+    "orbfe_bow_transform": (i32, [vp, vp, i32, i32, vp, vp, vp, vp, C.POINTER(i32), vp, vp, vp, C.POINTER(i32)]),
+    "orbfe_bow_device_views": (i32, [vp] + [C.POINTER(vp)] * 9),
     "orbfe_distinctive_descriptors_device": (i32, [i32, vp, vp, i32, vp, vp, vp]),
     "orbfe_distinctive_descriptors": (i32, [i32, vp, vp, i32, vp, vp]),
     "orbfe_search_by_projection_device": (i32, [i32, i32, i32, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, C.c_float, vp, vp, vp]),

@@ -1,0 +1,70 @@
+"""Host-side mirror of the bag-of-words assignment over the C ABI: ORBVocabulary (DBoW2
+TemplatedVocabulary<FORB::TDescriptor, FORB>) and its transform(features, BowVector, FeatureVector, levelsup) as called by
+Frame::ComputeBoW (/root/reference/src/Frame.cc:724-731; Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1125-1260)."""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from ._lib import check, ptr
+
+L1_NORM, L2_NORM, CHI_SQUARE, KL, BHATTACHARYYA, DOT_PRODUCT = range(6)   # DBoW2::ScoringType (BowVector.h:48-56)
+TF_IDF, TF, IDF, BINARY = range(4)                                       # DBoW2::WeightingType (BowVector.h:39-45)
+
+
+class ORBVocabulary:
+    """Built from the rows of the vocabulary text file (parent, is_leaf, 32 descriptor bytes, weight per node, file order)."""
+
+    def __init__(self, k, L, scoring, weighting, parent, is_leaf, desc, weight, max_features=4096, max_batch=1, device=0):
+        parent = np.ascontiguousarray(parent, np.int32)
+        is_leaf = np.ascontiguousarray(is_leaf, np.uint8)
+        desc = np.ascontiguousarray(desc, np.uint8)
+        weight = np.ascontiguousarray(weight, np.float64)
+        self.max_features, self.max_batch = max_features, max_batch
+        self._L = _lib.lib()
+        self._h = C.c_void_p()
+        check(self._L.orbfe_vocabulary_create(device, k, L, scoring, weighting, parent.shape[0], ptr(parent), ptr(is_leaf), ptr(desc), ptr(weight),
+                                              max_features, max_batch, C.byref(self._h)))
+
+    @property
+    def handle(self):
+        return self._h
+
+    def close(self):
+        if getattr(self, "_h", None) and self._h.value:
+            self._L.orbfe_vocabulary_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def words(self):
+        return self._L.orbfe_vocabulary_words(self._h)
+
+    def _fetch(self, frame, n):
+        F = self.max_features
+        wid, nid = np.zeros(n, np.int32), np.zeros(n, np.int32)
+        bw, bv = np.zeros(F, np.int32), np.zeros(F, np.float64)
+        fn, fs, ff = np.zeros(F, np.int32), np.zeros(F + 1, np.int32), np.zeros(F, np.int32)
+        nb, nf = C.c_int(0), C.c_int(0)
+        check(self._L.orbfe_bow_result(self._h, frame, n, ptr(wid), ptr(nid), ptr(bw), ptr(bv), C.byref(nb), ptr(fn), ptr(fs), ptr(ff), C.byref(nf)))
+        nb, nf = nb.value, nf.value
+        feat_vec = {int(fn[e]): ff[fs[e]:fs[e + 1]].copy() for e in range(nf)}
+        return {"word_ids": wid, "node_ids": nid, "bow_words": bw[:nb].copy(), "bow_values": bv[:nb].copy(), "feat_vec": feat_vec}
+
+    def transform(self, desc, levelsup=4):
+        """transform(features, BowVec, FeatVec, levelsup) for one frame's descriptors [n, 32] on the host."""
+        desc = np.ascontiguousarray(desc, np.uint8)
+        n = desc.shape[0]
+        check(self._L.orbfe_bow_transform(self._h, ptr(desc) if n else None, n, levelsup, None, None, None, None, None, None, None, None, None))
+        return self._fetch(0, n)
+
+    def transform_batch_device(self, d_desc, row_stride, d_counts, nframes, levelsup=4, stream=None):
+        check(self._L.orbfe_bow_transform_batch_device(self._h, C.c_void_p(d_desc), row_stride, C.c_void_p(d_counts), nframes, levelsup,
+                                                       C.c_void_p(stream) if stream else None))
+
+    def result(self, frame, nfeatures):
+        return self._fetch(frame, nfeatures)

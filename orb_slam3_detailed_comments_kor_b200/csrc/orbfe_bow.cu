@@ -1,0 +1,337 @@
+/* orbfe_bow.cu — bag-of-words assignment: Frame::ComputeBoW,
+ *   mpORBvocabulary->transform(vCurrentDesc, mBowVec, mFeatVec, 4)                    /root/reference/src/Frame.cc:724-731
+ *   TemplatedVocabulary::transform(features, BowVector&, FeatureVector&, levelsup)    Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1125-1193
+ *   TemplatedVocabulary::transform(feature, word_id, weight, nid, levelsup)           Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1217-1260
+ * for batches of frames whose descriptors are already on the device (the extractor's own output buffers can be passed as they are).
+ *
+ *   k_bow_descend    one thread = one descriptor: walk the vocabulary tree from the root, at every node take the child with the
+ *                    smallest Hamming distance (first child on ties, like the reference's strict `<`), remember the node passed
+ *                    at level L - levelsup, stop at a leaf -> (word id, node id, leaf node).
+ *   k_bow_assemble   one CTA = one frame: the std::map<WordId, WordValue> and std::map<NodeId, vector<unsigned>> of the reference
+ *                    are two shared-memory bitonic sorts of (id << 32 | feature index).  A word's value is its weight added once per
+ *                    feature in double precision (every addend of a word is the same number, so the order of the features does not
+ *                    matter); the L1 / L2 norm is accumulated by one thread in ascending word order, exactly the reference's
+ *                    loop over the map, then every entry is divided by it. */
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdint.h>
+#include <string.h>
+
+#include <algorithm>
+#include <new>
+#include <vector>
+
+#include "orbfe_internal.h"
+
+#define BOW_NT 256
+#define BOW_MAXF 4096
+
+struct orbfe_vocabulary {
+    int device, k, L, scoring, weighting, nnodes, nwords, maxFeatures, maxBatch;
+    /* tree (device): children of node i are childList[childStart[i] .. childStart[i+1]) */
+    int* childStart; int* childList; uint4* desc; double* weight; int* wordId;
+    /* results of the last batch (device), frame stride = maxFeatures */
+    int *featWord, *featNode, *featLeaf;
+    int *bowWords, *bowCount, *fvNodes, *fvStarts, *fvFeats, *fvCount;
+    double* bowValues;
+    uint8_t* stage; int* stageCount;   /* staging for the host entry point */
+    cudaStream_t stream;
+};
+
+static __device__ __forceinline__ int bow_ham(const uint4 qa, const uint4 qb, const uint4 a, const uint4 b) {
+    return __popc(qa.x ^ a.x) + __popc(qa.y ^ a.y) + __popc(qa.z ^ a.z) + __popc(qa.w ^ a.w) + __popc(qb.x ^ b.x) + __popc(qb.y ^ b.y) +
+           __popc(qb.z ^ b.z) + __popc(qb.w ^ b.w);
+}
+
+__global__ void __launch_bounds__(BOW_NT) k_bow_descend(const uint4* __restrict__ features, int rowStride, const int* __restrict__ counts, int maxF,
+                                                        const int* __restrict__ childStart, const int* __restrict__ childList,
+                                                        const uint4* __restrict__ ndesc, const int* __restrict__ wordId, int nidLevel,
+                                                        int* __restrict__ featWord, int* __restrict__ featNode, int* __restrict__ featLeaf) {
+    const int f = blockIdx.y, i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= min(counts[f], maxF)) return;
+    const uint4* q = features + ((size_t)f * rowStride + i) * 2;
+    const uint4 qa = __ldg(q), qb = __ldg(q + 1);
+    int node = 0, level = 0, nid = 0;
+    for (;;) {
+        const int c0 = __ldg(childStart + node), c1 = __ldg(childStart + node + 1);
+        if (c0 == c1) break;                       /* isLeaf() */
+        ++level;
+        int best = __ldg(childList + c0);
+        int bestD = bow_ham(qa, qb, __ldg(ndesc + 2 * best), __ldg(ndesc + 2 * best + 1));
+        for (int c = c0 + 1; c < c1; c++) {
+            const int id = __ldg(childList + c);
+            const int d = bow_ham(qa, qb, __ldg(ndesc + 2 * id), __ldg(ndesc + 2 * id + 1));
+            if (d < bestD) { bestD = d; best = id; }
+        }
+        node = best;
+        if (level == nidLevel) nid = node;
+    }
+    const size_t o = (size_t)f * maxF + i;
+    featWord[o] = __ldg(wordId + node);
+    featNode[o] = nid;
+    featLeaf[o] = node;
+}
+
+/* ascending bitonic sort of P (power of two) 64-bit keys in shared memory by the whole CTA */
+static __device__ void bow_sort(unsigned long long* key, int P) {
+    for (int k = 2; k <= P; k <<= 1)
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            __syncthreads();
+            for (int t = threadIdx.x; t < (P >> 1); t += BOW_NT) {
+                const int lo = ((t & ~(j - 1)) << 1) | (t & (j - 1)), hi = lo | j;
+                const unsigned long long a = key[lo], b = key[hi];
+                const bool up = (lo & k) == 0;
+                if ((a > b) == up) { key[lo] = b; key[hi] = a; }
+            }
+        }
+    __syncthreads();
+}
+
+/* Runs of equal ids in the sorted keys -> entry index of every run head; returns the number of runs.  entry[j] receives the
+ * index for heads and -1 otherwise. */
+static __device__ int bow_runs(const unsigned long long* key, int nvalid, int P, int* entry, int* warpTmp) {
+    const int per = (P + BOW_NT - 1) / BOW_NT, beg = threadIdx.x * per, end = min(beg + per, nvalid);
+    int cnt = 0;
+    for (int j = beg; j < end; j++) cnt += (j == 0 || (key[j] >> 32) != (key[j - 1] >> 32)) ? 1 : 0;
+    int incl = cnt;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += t;
+    }
+    if (lane == 31) warpTmp[warp] = incl;
+    __syncthreads();
+    int base = incl - cnt, total = 0;
+    for (int w = 0; w < BOW_NT / 32; w++) { if (w < warp) base += warpTmp[w]; total += warpTmp[w]; }
+    for (int j = beg; j < end; j++) {
+        const bool head = j == 0 || (key[j] >> 32) != (key[j - 1] >> 32);
+        entry[j] = head ? base++ : -1;
+    }
+    __syncthreads();
+    return total;
+}
+
+__global__ void __launch_bounds__(BOW_NT) k_bow_assemble(const int* __restrict__ counts, int maxF, const double* __restrict__ nodeWeight, int weighting,
+                                                         int norm /* 0 none, 1 L1, 2 L2 */, const int* __restrict__ featWord, const int* __restrict__ featNode,
+                                                         const int* __restrict__ featLeaf, int* __restrict__ bowWords, double* __restrict__ bowValues,
+                                                         int* __restrict__ bowCount, int* __restrict__ fvNodes, int* __restrict__ fvStarts,
+                                                         int* __restrict__ fvFeats, int* __restrict__ fvCount) {
+    extern __shared__ __align__(16) unsigned char bow_raw[];
+    unsigned long long* key = reinterpret_cast<unsigned long long*>(bow_raw);      /* P entries */
+    __shared__ int warpTmp[BOW_NT / 32];
+    __shared__ double s_norm;
+    const int f = blockIdx.x, tid = threadIdx.x;
+    const int n = min(counts[f], maxF);
+    int P = 32;
+    while (P < n) P <<= 1;
+    int* entry = reinterpret_cast<int*>(key + P);                                   /* P entries */
+    const size_t fo = (size_t)f * maxF;
+    /* ---- BowVector ---- */
+    int myValid = 0;
+    for (int i = tid; i < P; i += BOW_NT) {
+        unsigned long long kk = ~0ull;
+        if (i < n && nodeWeight[featLeaf[fo + i]] > 0) { kk = ((unsigned long long)(unsigned)featWord[fo + i] << 32) | (unsigned)i; myValid++; }
+        key[i] = kk;
+    }
+    /* block sum of myValid */
+    int v = myValid;
+#pragma unroll
+    for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if ((tid & 31) == 0) warpTmp[tid >> 5] = v;
+    __syncthreads();
+    int nv = 0;
+    for (int w = 0; w < BOW_NT / 32; w++) nv += warpTmp[w];
+    __syncthreads();
+    bow_sort(key, P);
+    const int nb = bow_runs(key, nv, P, entry, warpTmp);
+    for (int j = tid; j < nv; j += BOW_NT) {
+        const int e = entry[j];
+        if (e < 0) continue;
+        const unsigned word = (unsigned)(key[j] >> 32);
+        const double w = nodeWeight[featLeaf[fo + (unsigned)(key[j] & 0xffffffffu)]];
+        double val = w;
+        if (weighting <= 1)                                           /* TF_IDF, TF: addWeight once per feature of the word */
+            for (int t = j + 1; t < nv && (unsigned)(key[t] >> 32) == word; t++) val += w;
+        if (weighting <= 1 && norm == 0) val /= (double)nb;           /* the `!must` branch: divide by v.size() */
+        bowWords[fo + e] = (int)word;
+        bowValues[fo + e] = val;
+    }
+    __syncthreads();
+    if (norm != 0) {
+        if (tid == 0) {
+            double s = 0.0;
+            if (norm == 1) for (int e = 0; e < nb; e++) s += fabs(bowValues[fo + e]);
+            else { for (int e = 0; e < nb; e++) s += bowValues[fo + e] * bowValues[fo + e]; s = sqrt(s); }
+            s_norm = s;
+        }
+        __syncthreads();
+        const double s = s_norm;
+        if (s > 0.0)
+            for (int e = tid; e < nb; e += BOW_NT) bowValues[fo + e] = bowValues[fo + e] / s;
+    }
+    if (tid == 0) bowCount[f] = nb;
+    __syncthreads();
+    /* ---- FeatureVector ---- */
+    for (int i = tid; i < P; i += BOW_NT) {
+        unsigned long long kk = ~0ull;
+        if (i < n && nodeWeight[featLeaf[fo + i]] > 0) kk = ((unsigned long long)(unsigned)featNode[fo + i] << 32) | (unsigned)i;
+        key[i] = kk;
+    }
+    bow_sort(key, P);
+    const int nn = bow_runs(key, nv, P, entry, warpTmp);
+    const size_t so = (size_t)f * (maxF + 1);
+    for (int j = tid; j < nv; j += BOW_NT) {
+        fvFeats[fo + j] = (int)(unsigned)(key[j] & 0xffffffffu);
+        const int e = entry[j];
+        if (e >= 0) { fvNodes[fo + e] = (int)(unsigned)(key[j] >> 32); fvStarts[so + e] = j; }
+    }
+    if (tid == 0) { fvStarts[so + nn] = nv; fvCount[f] = nn; }
+}
+
+static int bow_norm_of(int scoring) { return scoring == 5 ? 0 : (scoring == 1 ? 2 : 1); }   /* ScoringObject.h:73-90 */
+
+extern "C" {
+
+void orbfe_vocabulary_destroy(orbfe_vocabulary* v) {
+    if (!v) return;
+    cudaSetDevice(v->device);
+    if (v->stream) cudaStreamSynchronize(v->stream);
+    void* bufs[] = {v->childStart, v->childList, v->desc, v->weight, v->wordId, v->featWord, v->featNode, v->featLeaf, v->bowWords, v->bowCount,
+                    v->fvNodes, v->fvStarts, v->fvFeats, v->fvCount, v->bowValues, v->stage, v->stageCount};
+    for (void* b : bufs) cudaFree(b);
+    if (v->stream) cudaStreamDestroy(v->stream);
+    delete v;
+}
+
+int orbfe_vocabulary_create(int device, int k, int L, int scoring, int weighting, int nrows, const int32_t* parent, const uint8_t* is_leaf,
+                            const uint8_t* desc, const double* weight, int max_features, int max_batch, orbfe_vocabulary** out) {
+    if (!out || !parent || !is_leaf || !desc || !weight || nrows < 1 || k < 0 || k > 20 || L < 1 || L > 10 || scoring < 0 || scoring > 5 ||
+        weighting < 0 || weighting > 3 || max_batch < 1) { orbfe_set_error("bad argument"); return ORBFE_E_INVALID; }   /* limits of loadFromTextFile (:1359) */
+    if (max_features < 1 || max_features > BOW_MAXF) { orbfe_set_error("at most %d features per frame", BOW_MAXF); return ORBFE_E_CAPACITY; }
+    *out = nullptr;
+    const int nn = nrows + 1;
+    std::vector<int> cnt(nn + 1, 0), start(nn + 1, 0), list(nrows), wid(nn, 0);
+    for (int r = 0; r < nrows; r++) {
+        if (parent[r] < 0 || parent[r] > r) { orbfe_set_error("row %d: parent %d does not precede the node", r, parent[r]); return ORBFE_E_INVALID; }
+        cnt[parent[r]]++;
+    }
+    for (int i = 0; i < nn; i++) start[i + 1] = start[i] + cnt[i];
+    std::vector<int> cur(start.begin(), start.end() - 1);
+    int nwords = 0;
+    for (int r = 0; r < nrows; r++) {
+        list[cur[parent[r]]++] = r + 1;
+        if ((is_leaf[r] != 0) != (cnt[r + 1] == 0)) { orbfe_set_error("row %d: leaf flag and child list disagree", r); return ORBFE_E_INVALID; }
+        if (is_leaf[r]) wid[r + 1] = nwords++;
+    }
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev) {
+        orbfe_set_error("no usable CUDA device %d (found %d); this library has no CPU path", device, ndev);
+        return ORBFE_E_CUDA;
+    }
+    ORBFE_CUDA(cudaSetDevice(device));
+    orbfe_vocabulary* v = new (std::nothrow) orbfe_vocabulary();
+    if (!v) return ORBFE_E_INVALID;
+    memset(v, 0, sizeof(*v));
+    v->device = device; v->k = k; v->L = L; v->scoring = scoring; v->weighting = weighting; v->nnodes = nn; v->nwords = nwords;
+    v->maxFeatures = max_features; v->maxBatch = max_batch;
+    std::vector<uint8_t> nd((size_t)nn * 32, 0);
+    memcpy(nd.data() + 32, desc, (size_t)nrows * 32);
+    std::vector<double> nw(nn, 0.0);
+    memcpy(nw.data() + 1, weight, (size_t)nrows * sizeof(double));
+    const size_t fr = (size_t)max_batch * max_features;
+    cudaError_t e = cudaStreamCreateWithFlags(&v->stream, cudaStreamNonBlocking);
+#define BOW_ALLOC(p, bytes) if (e == cudaSuccess) e = cudaMalloc((void**)&(p), (bytes))
+    BOW_ALLOC(v->childStart, (size_t)(nn + 1) * 4); BOW_ALLOC(v->childList, (size_t)std::max(nrows, 1) * 4); BOW_ALLOC(v->desc, (size_t)nn * 32);
+    BOW_ALLOC(v->weight, (size_t)nn * 8); BOW_ALLOC(v->wordId, (size_t)nn * 4);
+    BOW_ALLOC(v->featWord, fr * 4); BOW_ALLOC(v->featNode, fr * 4); BOW_ALLOC(v->featLeaf, fr * 4);
+    BOW_ALLOC(v->bowWords, fr * 4); BOW_ALLOC(v->bowValues, fr * 8); BOW_ALLOC(v->bowCount, (size_t)max_batch * 4);
+    BOW_ALLOC(v->fvNodes, fr * 4); BOW_ALLOC(v->fvStarts, (size_t)max_batch * (max_features + 1) * 4); BOW_ALLOC(v->fvFeats, fr * 4);
+    BOW_ALLOC(v->fvCount, (size_t)max_batch * 4); BOW_ALLOC(v->stage, (size_t)max_features * 32); BOW_ALLOC(v->stageCount, 4);
+#undef BOW_ALLOC
+    if (e == cudaSuccess) e = cudaMemcpy(v->childStart, start.data(), (size_t)(nn + 1) * 4, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(v->childList, list.data(), (size_t)nrows * 4, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(v->desc, nd.data(), (size_t)nn * 32, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(v->weight, nw.data(), (size_t)nn * 8, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(v->wordId, wid.data(), (size_t)nn * 4, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_bow_assemble, cudaFuncAttributeMaxDynamicSharedMemorySize, BOW_MAXF * 12);
+    if (e != cudaSuccess) { const int rc = orbfe_cuda_fail(e, "vocabulary allocation"); orbfe_vocabulary_destroy(v); return rc; }
+    *out = v;
+    return ORBFE_OK;
+}
+
+int orbfe_vocabulary_words(const orbfe_vocabulary* v) { return v ? v->nwords : 0; }
+
+int orbfe_bow_transform_batch_device(orbfe_vocabulary* v, const uint8_t* d_desc, int row_stride, const int32_t* d_counts, int nframes, int levelsup,
+                                     void* stream) {
+    if (!v || !d_desc || !d_counts || nframes < 1 || row_stride < 1) { orbfe_set_error("bad argument"); return ORBFE_E_INVALID; }
+    if (nframes > v->maxBatch) { orbfe_set_error("batch of %d frames exceeds max_batch %d", nframes, v->maxBatch); return ORBFE_E_CAPACITY; }
+    if ((uintptr_t)d_desc & 15) { orbfe_set_error("descriptor array must be 16-byte aligned"); return ORBFE_E_INVALID; }
+    ORBFE_CUDA(cudaSetDevice(v->device));
+    cudaStream_t st = stream ? (cudaStream_t)stream : v->stream;
+    const int F = v->maxFeatures;
+    k_bow_descend<<<dim3((F + BOW_NT - 1) / BOW_NT, nframes), BOW_NT, 0, st>>>((const uint4*)d_desc, row_stride, d_counts, F, v->childStart, v->childList, v->desc,
+                                                                               v->wordId, v->L - levelsup, v->featWord, v->featNode, v->featLeaf);
+    int P = 32;
+    while (P < F) P <<= 1;
+    k_bow_assemble<<<nframes, BOW_NT, (size_t)P * 12, st>>>(d_counts, F, v->weight, v->weighting, bow_norm_of(v->scoring), v->featWord, v->featNode, v->featLeaf,
+                                                           v->bowWords, v->bowValues, v->bowCount, v->fvNodes, v->fvStarts, v->fvFeats, v->fvCount);
+    ORBFE_CUDA(cudaGetLastError());
+    return ORBFE_OK;
+}
+
+int orbfe_bow_result(orbfe_vocabulary* v, int frame, int nfeatures, int32_t* word_ids, int32_t* node_ids, int32_t* bow_words, double* bow_values,
+                     int32_t* nbow, int32_t* fv_nodes, int32_t* fv_starts, int32_t* fv_feats, int32_t* nfv) {
+    if (!v || frame < 0 || frame >= v->maxBatch || nfeatures < 0 || nfeatures > v->maxFeatures) { orbfe_set_error("bad argument"); return ORBFE_E_INVALID; }
+    ORBFE_CUDA(cudaSetDevice(v->device));
+    ORBFE_CUDA(cudaDeviceSynchronize());
+    const size_t fo = (size_t)frame * v->maxFeatures, so = (size_t)frame * (v->maxFeatures + 1);
+    int nb = 0, nn = 0;
+    ORBFE_CUDA(cudaMemcpy(&nb, v->bowCount + frame, 4, cudaMemcpyDeviceToHost));
+    ORBFE_CUDA(cudaMemcpy(&nn, v->fvCount + frame, 4, cudaMemcpyDeviceToHost));
+    if (nbow) *nbow = nb;
+    if (nfv) *nfv = nn;
+    if (word_ids && nfeatures) ORBFE_CUDA(cudaMemcpy(word_ids, v->featWord + fo, (size_t)nfeatures * 4, cudaMemcpyDeviceToHost));
+    if (node_ids && nfeatures) ORBFE_CUDA(cudaMemcpy(node_ids, v->featNode + fo, (size_t)nfeatures * 4, cudaMemcpyDeviceToHost));
+    if (bow_words && nb) ORBFE_CUDA(cudaMemcpy(bow_words, v->bowWords + fo, (size_t)nb * 4, cudaMemcpyDeviceToHost));
+    if (bow_values && nb) ORBFE_CUDA(cudaMemcpy(bow_values, v->bowValues + fo, (size_t)nb * 8, cudaMemcpyDeviceToHost));
+    if (fv_nodes && nn) ORBFE_CUDA(cudaMemcpy(fv_nodes, v->fvNodes + fo, (size_t)nn * 4, cudaMemcpyDeviceToHost));
+    if (fv_starts) ORBFE_CUDA(cudaMemcpy(fv_starts, v->fvStarts + so, (size_t)(nn + 1) * 4, cudaMemcpyDeviceToHost));
+    if (fv_feats && nn) {
+        int total = 0;
+        ORBFE_CUDA(cudaMemcpy(&total, v->fvStarts + so + nn, 4, cudaMemcpyDeviceToHost));
+        if (total) ORBFE_CUDA(cudaMemcpy(fv_feats, v->fvFeats + fo, (size_t)total * 4, cudaMemcpyDeviceToHost));
+    }
+    return ORBFE_OK;
+}
+
+int orbfe_bow_transform(orbfe_vocabulary* v, const uint8_t* desc, int n, int levelsup, int32_t* word_ids, int32_t* node_ids, int32_t* bow_words,
+                        double* bow_values, int32_t* nbow, int32_t* fv_nodes, int32_t* fv_starts, int32_t* fv_feats, int32_t* nfv) {
+    if (!v || (n > 0 && !desc) || n < 0) { orbfe_set_error("bad argument"); return ORBFE_E_INVALID; }
+    if (n > v->maxFeatures) { orbfe_set_error("%d features exceed max_features %d", n, v->maxFeatures); return ORBFE_E_CAPACITY; }
+    ORBFE_CUDA(cudaSetDevice(v->device));
+    if (n) ORBFE_CUDA(cudaMemcpyAsync(v->stage, desc, (size_t)n * 32, cudaMemcpyHostToDevice, v->stream));
+    ORBFE_CUDA(cudaMemcpyAsync(v->stageCount, &n, 4, cudaMemcpyHostToDevice, v->stream));
+    int rc = orbfe_bow_transform_batch_device(v, v->stage, v->maxFeatures, v->stageCount, 1, levelsup, v->stream);
+    if (rc) return rc;
+    ORBFE_CUDA(cudaStreamSynchronize(v->stream));
+    return orbfe_bow_result(v, 0, n, word_ids, node_ids, bow_words, bow_values, nbow, fv_nodes, fv_starts, fv_feats, nfv);
+}
+
+int orbfe_bow_device_views(orbfe_vocabulary* v, const int32_t** d_feat_word, const int32_t** d_feat_node, const int32_t** d_bow_words,
+                           const double** d_bow_values, const int32_t** d_bow_count, const int32_t** d_fv_nodes, const int32_t** d_fv_starts,
+                           const int32_t** d_fv_feats, const int32_t** d_fv_count) {
+    if (!v) return ORBFE_E_INVALID;
+    if (d_feat_word) *d_feat_word = v->featWord;
+    if (d_feat_node) *d_feat_node = v->featNode;
+    if (d_bow_words) *d_bow_words = v->bowWords;
+    if (d_bow_values) *d_bow_values = v->bowValues;
+    if (d_bow_count) *d_bow_count = v->bowCount;
+    if (d_fv_nodes) *d_fv_nodes = v->fvNodes;
+    if (d_fv_starts) *d_fv_starts = v->fvStarts;
+    if (d_fv_feats) *d_fv_feats = v->fvFeats;
+    if (d_fv_count) *d_fv_count = v->fvCount;
+    return ORBFE_OK;
+}
+
+}  /* extern "C" */

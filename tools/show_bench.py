@@ -17,3 +17,4 @@ for l in sys.stdin:
     print("hamming %.3e pairs/s  ms %.3f  frac %.3f" % (h.get("value", 0), h.get("ms_per_step", 0), (h.get("roofline") or {}).get("frac", 0)))
     print("clocks", d.get("clocks"), "cpu", d.get("cpu_baseline"))
     print("projection", d.get("projection"), "| rectify %.0f frames/s" % (d.get("rectify") or {}).get("value", 0))
+    print("bow", d.get("bow"))
