@@ -228,10 +228,12 @@ int orbfe_distinctive_descriptors(int device, const uint8_t* desc, const int32_t
                                   int32_t* best_median);
 
 /* ------------------------------------------------------------------------------- projection-gated search (N1) */
-/* Replaces the search of Tracking::SearchLocalPoints (src/Tracking.cc:3430-3524):
+/* Replaces the searches of Tracking::SearchLocalPoints (src/Tracking.cc:3430-3524) and Tracking::TrackWithMotionModel:
  *   int ORBmatcher::SearchByProjection(Frame &F, const vector<MapPoint*> &vpMapPoints, const float th, const bool bFarPoints,
  *                                      const float thFarPoints)                                   (src/ORBmatcher.cc:44-214)
- * including the frame grid it walks: Frame::AssignFeaturesToGrid / PosInGrid (src/Frame.cc:380-411, 711-721; 64 x 48 cells,
+ *   int ORBmatcher::SearchByProjection(Frame &CurrentFrame, const Frame &LastFrame, const float th, const bool bMono)
+ *                                      (src/ORBmatcher.cc:2193-2419; queries flagged ORBFE_PQ_BEST_ONLY, check_orientation = mbCheckOrientation)
+ * including the frame grid they walk: Frame::AssignFeaturesToGrid / PosInGrid (src/Frame.cc:380-411, 711-721; 64 x 48 cells,
  * include/Frame.h:37-38) and Frame::GetFeaturesInArea (src/Frame.cc:643-709).  The result is the reference's, including its
  * serial rule that a matched map point occupies its keypoint for the map points after it. */
 typedef struct orbfe_frame_grid {   /* Frame::mnMinX, mnMinY, mfGridElementWidthInv, mfGridElementHeightInv */
@@ -243,22 +245,28 @@ typedef struct orbfe_frame_grid {   /* Frame::mnMinX, mnMinY, mfGridElementWidth
 #define ORBFE_PQ_SKIP 4        /* not in view / bad / too far (:52-59): no search */
 #define ORBFE_PQ_AFTER_LEFT 8  /* right-camera half (:145-211) of the map point of the query before: not run when that one
                                   failed the ratio test (the `continue` at :117-118 leaves the whole iteration) */
+#define ORBFE_PQ_BEST_ONLY 16  /* frame-to-frame rule (:2267-2300): accepted iff bestDist <= TH_HIGH, no second-best test */
+#define ORBFE_PQ_NEEDS_LEFT_WINDOW 32 /* right-camera half (:2325-2386) of the query before: not run when that one's window holds
+                                  no keypoint (`if(vIndices2.empty()) continue;` at :2262-2263) */
 typedef struct orbfe_proj_query {   /* one (map point, camera) search, in the reference's loop order */
     float x, y;        /* mTrackProjX, mTrackProjY (mTrackProjXR, mTrackProjYR with ORBFE_PQ_RIGHT) */
     float radius;      /* RadiusByViewingCos(mTrackViewCos) [* th] * F.mvScaleFactors[nPredictedLevel] (:67-73) */
     float xr;          /* mTrackProjXR, for the |xr - mvuRight| gate (:95-100); read only when u_right is given */
-    int32_t min_level; /* nPredictedLevel - 1 */
-    int32_t max_level; /* nPredictedLevel */
+    int32_t min_level; /* nPredictedLevel - 1        (frame-to-frame: nLastOctave / 0 / nLastOctave-1, :2253-2258) */
+    int32_t max_level; /* nPredictedLevel; -1 = open (frame-to-frame: -1 / nLastOctave / nLastOctave+1) */
     int32_t flags;     /* ORBFE_PQ_* */
+    float angle;       /* kpLF.angle (:2314), read only with check_orientation */
 } orbfe_proj_query;
 
-#define ORBFE_PS_NO_CANDIDATES 0   /* empty window, or every candidate occupied / gated out */
+#define ORBFE_PS_NO_CANDIDATES 0   /* every keypoint of the window is occupied or gated out by mvuRight */
 #define ORBFE_PS_ACCEPTED 1
 #define ORBFE_PS_OVER_THRESHOLD 2  /* bestDist > TH_HIGH */
 #define ORBFE_PS_RATIO_REJECTED 3  /* bestLevel == bestLevel2 && bestDist > mfNNratio * bestDist2 */
 #define ORBFE_PS_SKIPPED 4         /* ORBFE_PQ_SKIP */
 #define ORBFE_PS_CAPACITY 5        /* the frame holds more keypoints than promised: nothing was searched */
-#define ORBFE_PS_DROPPED 6         /* ORBFE_PQ_AFTER_LEFT and the left half was ratio-rejected */
+#define ORBFE_PS_DROPPED 6         /* ORBFE_PQ_AFTER_LEFT / ORBFE_PQ_NEEDS_LEFT_WINDOW and the left half ended the iteration */
+#define ORBFE_PS_ROTATION 7        /* matched, then removed by the rotation-consistency histogram (:2391-2412) */
+#define ORBFE_PS_EMPTY_WINDOW 8    /* GetFeaturesInArea returned nothing */
 typedef struct orbfe_proj_match {
     int32_t best_idx;      /* bestIdx as a row of the frame's keypoint array (right camera: local index + n_left); -1 if none */
     int32_t best_dist, best_level, second_dist, second_level;   /* bestDist, bestLevel, bestDist2, bestLevel2 (256 / -1 when unset) */
@@ -274,17 +282,20 @@ typedef struct orbfe_proj_match {
  *   d_partner: per row the row matched in the other camera (mvLeftToRightMatch[i] + Nleft / mvRightToLeftMatch[i - Nleft]) or
  *     -1, or NULL;   d_taken_in: per row, nonzero iff F.mvpMapPoints[row] has observations (NULL: none);
  *   d_queries / d_qdesc (pMP->GetDescriptor()): frame f = entries [d_q_offsets[f], d_q_offsets[f+1]);
- *   th_high = ORBmatcher::TH_HIGH (100), nnratio = mfNNratio;   d_taken_out (may be NULL or d_taken_in): occupancy afterwards. */
+ *   th_high = ORBmatcher::TH_HIGH (100), nnratio = mfNNratio;   d_taken_out (may be NULL or d_taken_in): occupancy afterwards;
+ *   check_orientation != 0: after the searches, the rotation histogram of (query angle - keypoint angle) over the frame's matches
+ *     (30 bins, ComputeThreeMaxima, src/ORBmatcher.cc:2545-2586) removes the matches outside the three fullest bins. */
 int orbfe_search_by_projection_device(int device, int nframes, int max_keypoints, const orbfe_keypoint* d_kps, const uint8_t* d_desc,
                                       const int32_t* d_kp_offsets, const int32_t* d_n_left, const float* d_u_right, const int32_t* d_partner,
                                       const uint8_t* d_taken_in, const orbfe_frame_grid* d_grids, const orbfe_proj_query* d_queries,
-                                      const uint8_t* d_qdesc, const int32_t* d_q_offsets, int th_high, float nnratio, orbfe_proj_match* d_out,
-                                      uint8_t* d_taken_out, void* stream);
+                                      const uint8_t* d_qdesc, const int32_t* d_q_offsets, int th_high, float nnratio, int check_orientation,
+                                      orbfe_proj_match* d_out, uint8_t* d_taken_out, void* stream);
 /* One frame over host memory (copies inside, synchronous).  taken is updated in place (may be NULL); *nmatches receives the
  * reference's return value (an accepted row with a stereo partner counts twice). */
 int orbfe_search_by_projection(int device, const orbfe_keypoint* kps, const uint8_t* desc, int n, int n_left, const float* u_right,
                                const int32_t* partner, uint8_t* taken, const orbfe_frame_grid* grid, const orbfe_proj_query* queries,
-                               const uint8_t* qdesc, int nq, int th_high, float nnratio, orbfe_proj_match* out, int* nmatches);
+                               const uint8_t* qdesc, int nq, int th_high, float nnratio, int check_orientation, orbfe_proj_match* out,
+                               int* nmatches);
 
 /* ------------------------------------------------------------------------------------------ input conditioning */
 /* The steps the example drivers and Tracking run on each image before the extractor, so that an

@@ -83,7 +83,9 @@ inline void FishEyeKnnMatches(const cv::Mat& stereoDescLeft, const cv::Mat& ster
 }
 
 /* The loop of ORBmatcher::SearchByProjection(Frame &F, const vector<MapPoint*> &vpMapPoints, th, bFarPoints, thFarPoints)
- * (src/ORBmatcher.cc:44-214) on the frame's arrays; the grid of Frame::AssignFeaturesToGrid is rebuilt on the GPU.
+ * (src/ORBmatcher.cc:44-214) — or, with ORBFE_PQ_BEST_ONLY queries and checkOrientation = mbCheckOrientation, of
+ * SearchByProjection(Frame &CurrentFrame, const Frame &LastFrame, th, bMono) (:2193-2419) — on the frame's arrays; the grid of
+ * Frame::AssignFeaturesToGrid is rebuilt on the GPU.
  *   keys / descriptors: F.mvKeysUn + F.mDescriptors (Nleft == -1) or mvKeys followed by mvKeysRight (fisheye rig);
  *   uRight: &F.mvuRight or NULL;   partner: per row the row matched in the other camera or -1 (see orbfe.h), or NULL;
  *   taken[row] != 0 iff F.mvpMapPoints[row] has observations — updated in place;
@@ -94,7 +96,8 @@ inline void FishEyeKnnMatches(const cv::Mat& stereoDescLeft, const cv::Mat& ster
 inline int SearchByProjection(const std::vector<cv::KeyPoint>& keys, const cv::Mat& descriptors, int Nleft, const std::vector<float>* uRight,
                               const std::vector<int>* partner, std::vector<unsigned char>& taken, float mnMinX, float mnMinY,
                               float mfGridElementWidthInv, float mfGridElementHeightInv, const std::vector<orbfe_proj_query>& queries,
-                              const cv::Mat& queryDescriptors, float mfNNratio, std::vector<orbfe_proj_match>& out, int device = 0) {
+                              const cv::Mat& queryDescriptors, float mfNNratio, std::vector<orbfe_proj_match>& out, bool checkOrientation = false,
+                              int device = 0) {
     static_assert(sizeof(cv::KeyPoint) == sizeof(orbfe_keypoint), "cv::KeyPoint layout");
     const int n = (int)keys.size(), nq = (int)queries.size();
     out.resize(nq);
@@ -106,7 +109,7 @@ inline int SearchByProjection(const std::vector<cv::KeyPoint>& keys, const cv::M
     int nmatches = 0;
     if (orbfe_search_by_projection(device, reinterpret_cast<const orbfe_keypoint*>(keys.data()), d.data(), n, Nleft, uRight ? uRight->data() : nullptr,
                                    partner ? partner->data() : nullptr, taken.data(), &grid, queries.data(), qd.data(), nq, ORBmatcher::TH_HIGH,
-                                   mfNNratio, out.data(), &nmatches) != ORBFE_OK)
+                                   mfNNratio, checkOrientation ? 1 : 0, out.data(), &nmatches) != ORBFE_OK)
         throw std::runtime_error(std::string("orbfe_search_by_projection: ") + orbfe_last_error());
     return nmatches;
 }

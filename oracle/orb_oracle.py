@@ -68,7 +68,7 @@ def lib():
     L.orc_vocabulary_words.argtypes = [vp]
     L.orc_bow_transform.argtypes = [vp, vp, C.c_int, C.c_int, vp, vp, vp, vp, vp, vp, vp, vp, vp]
     L.orc_distinctive_descriptors.argtypes = [vp, vp, C.c_int, vp, vp]
-    L.orc_search_by_projection.argtypes = [vp, vp, C.c_int, C.c_int, vp, vp, vp, vp, vp, vp, C.c_int, C.c_int, C.c_float, vp]
+    L.orc_search_by_projection.argtypes = [vp, vp, C.c_int, C.c_int, vp, vp, vp, vp, vp, vp, C.c_int, C.c_int, C.c_float, C.c_int, vp]
     L.orc_search_by_projection.restype = C.c_int
     L.orc_clahe_u8.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_double, C.c_int, C.c_int, vp, C.c_int, vp]
     L.orc_clahe_u8.restype = C.c_int
@@ -270,13 +270,15 @@ def distinctive_descriptors(desc, offsets):
 
 
 PROJ_QUERY_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("radius", "<f4"), ("xr", "<f4"), ("min_level", "<i4"), ("max_level", "<i4"),
-                             ("flags", "<i4")])
+                             ("flags", "<i4"), ("angle", "<f4")])
 PROJ_MATCH_DTYPE = np.dtype([("best_idx", "<i4"), ("best_dist", "<i4"), ("best_level", "<i4"), ("second_dist", "<i4"),
                              ("second_level", "<i4"), ("accepted", "<i4"), ("status", "<i4")])
 
 
-def search_by_projection(kps, desc, queries, qdesc, grid, n_left=-1, u_right=None, partner=None, taken=None, th_high=100, nnratio=0.8):
-    """ORBmatcher::SearchByProjection(Frame&, vpMapPoints, th) on arrays, serial.  Returns (matches, taken_after, nmatches)."""
+def search_by_projection(kps, desc, queries, qdesc, grid, n_left=-1, u_right=None, partner=None, taken=None, th_high=100, nnratio=0.8,
+                         check_orientation=False):
+    """ORBmatcher::SearchByProjection(Frame&, vpMapPoints, th) / (CurrentFrame, LastFrame, th, bMono) on arrays, serial.
+    Returns (matches, taken_after, nmatches)."""
     kps = np.ascontiguousarray(kps, KP_DTYPE)
     desc = np.ascontiguousarray(desc, np.uint8)
     queries = np.ascontiguousarray(queries, PROJ_QUERY_DTYPE)
@@ -288,7 +290,7 @@ def search_by_projection(kps, desc, queries, qdesc, grid, n_left=-1, u_right=Non
     out = np.zeros(queries.shape[0], PROJ_MATCH_DTYPE)
     nm = lib().orc_search_by_projection(_ptr(kps), _ptr(desc), kps.shape[0], n_left, _ptr(ur) if ur is not None else None,
                                         _ptr(pt) if pt is not None else None, _ptr(tk), _ptr(grid), _ptr(queries), _ptr(qdesc),
-                                        queries.shape[0], th_high, nnratio, _ptr(out))
+                                        queries.shape[0], th_high, nnratio, int(check_orientation), _ptr(out))
     return out, tk, nm
 
 

@@ -4,6 +4,8 @@
  *   /root/reference/src/Frame.cc:643-709    Frame::GetFeaturesInArea
  *   /root/reference/src/Frame.cc:711-721    Frame::PosInGrid
  *   /root/reference/src/ORBmatcher.cc:44-214 ORBmatcher::SearchByProjection(Frame&, const vector<MapPoint*>&, th, ...)
+ *   /root/reference/src/ORBmatcher.cc:2193-2419 ORBmatcher::SearchByProjection(Frame &CurrentFrame, const Frame &LastFrame, th, bMono)
+ *   /root/reference/src/ORBmatcher.cc:2545-2586 ORBmatcher::ComputeThreeMaxima
  * on plain arrays, in the reference's serial order (a map point that was matched blocks its keypoint for the map points
  * after it).  No third-party arithmetic is involved; parity unpinned beyond the independent Python restatement in
  * tools/make_goldens.py (tests/golden/projection.npz). */
@@ -26,18 +28,19 @@ extern "C" {
 
 /* Layout-identical to orbfe_frame_grid / orbfe_proj_query / orbfe_proj_match (include/orbfe.h). */
 typedef struct { float min_x, min_y, inv_w, inv_h; } orc_frame_grid;
-typedef struct { float x, y, radius, xr; int32_t min_level, max_level, flags; } orc_proj_query;
+typedef struct { float x, y, radius, xr; int32_t min_level, max_level, flags; float angle; } orc_proj_query;
 typedef struct { int32_t best_idx, best_dist, best_level, second_dist, second_level, accepted, status; } orc_proj_match;
 
-enum { PQ_RIGHT = 1, PQ_BLOCKS = 2, PQ_SKIP = 4, PQ_AFTER_LEFT = 8 };
-enum { PS_NO_CANDIDATES = 0, PS_ACCEPTED = 1, PS_OVER_THRESHOLD = 2, PS_RATIO_REJECTED = 3, PS_SKIPPED = 4, PS_DROPPED = 6 };
+enum { PQ_RIGHT = 1, PQ_BLOCKS = 2, PQ_SKIP = 4, PQ_AFTER_LEFT = 8, PQ_BEST_ONLY = 16, PQ_NEEDS_LEFT_WINDOW = 32 };
+enum { PS_NO_CANDIDATES = 0, PS_ACCEPTED = 1, PS_OVER_THRESHOLD = 2, PS_RATIO_REJECTED = 3, PS_SKIPPED = 4, PS_DROPPED = 6, PS_ROTATION = 7, PS_EMPTY_WINDOW = 8 };
+const int HISTO_LENGTH = 30; /* ORBmatcher.cc:38 */
 
 /* kps: n rows (rows >= n_left belong to the right camera when n_left >= 0); taken (in/out): rows whose map point has
  * observations; partner: row matched in the other camera or -1 (may be NULL); u_right may be NULL.
  * Returns nmatches as the reference counts them (a matched row with a partner counts twice). */
 int orc_search_by_projection(const orc_keypoint* kps, const uint8_t* desc, int n, int n_left, const float* u_right, const int32_t* partner,
                              uint8_t* taken, const orc_frame_grid* g, const orc_proj_query* q, const uint8_t* qdesc, int nq, int th_high,
-                             float nnratio, orc_proj_match* out) {
+                             float nnratio, int check_orientation, orc_proj_match* out) {
     Grid* grid = new Grid();
     /* AssignFeaturesToGrid + PosInGrid */
     for (int i = 0; i < n; i++) {
@@ -46,13 +49,16 @@ int orc_search_by_projection(const orc_keypoint* kps, const uint8_t* desc, int n
         grid->cell[(n_left >= 0 && i >= n_left) ? 1 : 0][posX][posY].push_back(i);
     }
     int nmatches = 0;
-    bool prevRatioRejected = false;
+    bool prevRatioRejected = false, prevWindowEmpty = false;
+    std::vector<int> rotHist[HISTO_LENGTH];            /* query indices; the reference stores the keypoint row */
+    const float factor = 1.0f / HISTO_LENGTH;
     for (int iq = 0; iq < nq; iq++) {
         const orc_proj_query& p = q[iq];
         orc_proj_match& o = out[iq];
         o.best_idx = -1; o.best_dist = 256; o.best_level = -1; o.second_dist = 256; o.second_level = -1; o.accepted = 0;
-        const bool dropped = (p.flags & PQ_AFTER_LEFT) && prevRatioRejected;
+        const bool dropped = ((p.flags & PQ_AFTER_LEFT) && prevRatioRejected) || ((p.flags & PQ_NEEDS_LEFT_WINDOW) && prevWindowEmpty);
         prevRatioRejected = false;
+        prevWindowEmpty = false;
         if (p.flags & PQ_SKIP) { o.status = PS_SKIPPED; continue; }
         if (dropped) { o.status = PS_DROPPED; continue; }
         const bool right = (p.flags & PQ_RIGHT) != 0;
@@ -80,7 +86,7 @@ int orc_search_by_projection(const orc_keypoint* kps, const uint8_t* desc, int n
                         if (std::fabs(distx) < r && std::fabs(disty) < r) vIndices.push_back(idx);
                     }
         } while (false);
-        if (vIndices.empty()) { o.status = PS_NO_CANDIDATES; continue; }
+        if (vIndices.empty()) { o.status = PS_EMPTY_WINDOW; prevWindowEmpty = !right; continue; }
         int bestDist = 256, bestLevel = -1, bestDist2 = 256, bestLevel2 = -1, bestIdx = -1;
         for (int idx : vIndices) {
             if (taken[idx]) continue;
@@ -98,7 +104,7 @@ int orc_search_by_projection(const orc_keypoint* kps, const uint8_t* desc, int n
         o.best_idx = bestIdx; o.best_dist = bestDist; o.best_level = bestLevel; o.second_dist = bestDist2; o.second_level = bestLevel2;
         if (bestIdx < 0) { o.status = PS_NO_CANDIDATES; continue; } /* every candidate was taken or failed the uRight gate */
         if (bestDist > th_high) { o.status = PS_OVER_THRESHOLD; continue; }
-        if (bestLevel == bestLevel2 && (float)bestDist > nnratio * (float)bestDist2) {
+        if (!(p.flags & PQ_BEST_ONLY) && bestLevel == bestLevel2 && (float)bestDist > nnratio * (float)bestDist2) {
             o.status = PS_RATIO_REJECTED;
             prevRatioRejected = !right; /* the `continue` at ORBmatcher.cc:117-118 also skips the right-camera half of this map point */
             continue;
@@ -110,6 +116,31 @@ int orc_search_by_projection(const orc_keypoint* kps, const uint8_t* desc, int n
             nmatches++;
             if (p.flags & PQ_BLOCKS) taken[partner[bestIdx]] = 1;
         }
+        if (check_orientation) {                               /* ORBmatcher.cc:2305-2322 */
+            float rot = p.angle - kps[bestIdx].angle;
+            if (rot < 0.0) rot += 360.0f;
+            int bin = (int)std::round(rot * factor);
+            if (bin == HISTO_LENGTH) bin = 0;
+            if (bin >= 0 && bin < HISTO_LENGTH) rotHist[bin].push_back(iq);
+        }
+    }
+    if (check_orientation) {                                   /* ORBmatcher.cc:2391-2412 with ComputeThreeMaxima (:2545-2586) */
+        int ind1 = -1, ind2 = -1, ind3 = -1, max1 = 0, max2 = 0, max3 = 0;
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            const int s = (int)rotHist[i].size();
+            if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = i; }
+            else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = i; }
+            else if (s > max3) { max3 = s; ind3 = i; }
+        }
+        if (max2 < 0.1f * (float)max1) { ind2 = -1; ind3 = -1; }
+        else if (max3 < 0.1f * (float)max1) { ind3 = -1; }
+        for (int i = 0; i < HISTO_LENGTH; i++)
+            if (i != ind1 && i != ind2 && i != ind3)
+                for (int iq : rotHist[i]) {
+                    out[iq].accepted = 0; out[iq].status = PS_ROTATION;
+                    taken[out[iq].best_idx] = 0;               /* mvpMapPoints[row] = NULL */
+                    nmatches -= 1 + ((n_left >= 0 && partner && partner[out[iq].best_idx] >= 0) ? 1 : 0);   /* what it had added */
+                }
     }
     delete grid;
     return nmatches;

@@ -1,6 +1,9 @@
-/* orbfe_project.cu — projection-gated descriptor search: the search of Tracking::SearchLocalPoints,
+/* orbfe_project.cu — projection-gated descriptor search: the searches of Tracking::SearchLocalPoints and
+ * Tracking::TrackWithMotionModel,
  *   ORBmatcher::SearchByProjection(Frame&, const vector<MapPoint*>&, th, bFarPoints, thFarPoints)   /root/reference/src/ORBmatcher.cc:44-214
- * together with the frame grid it walks,
+ *   ORBmatcher::SearchByProjection(Frame &CurrentFrame, const Frame &LastFrame, th, bMono)          /root/reference/src/ORBmatcher.cc:2193-2419
+ *     (best match only, then the rotation-consistency histogram with ComputeThreeMaxima, :2545-2586)
+ * together with the frame grid they walk,
  *   Frame::AssignFeaturesToGrid / PosInGrid   /root/reference/src/Frame.cc:380-411, 711-721   (64 x 48 cells, include/Frame.h:37-38)
  *   Frame::GetFeaturesInArea                  /root/reference/src/Frame.cc:643-709
  *
@@ -84,8 +87,8 @@ __global__ void __launch_bounds__(PJ_NT) k_search_by_projection(int maxKp, const
                                                                 const float* __restrict__ uRightAll, const int32_t* __restrict__ partnerAll,
                                                                 const uint8_t* __restrict__ takenIn, const orbfe_frame_grid* __restrict__ grids,
                                                                 const orbfe_proj_query* __restrict__ queries, const uint8_t* __restrict__ qdescAll,
-                                                                const int32_t* __restrict__ qOff, int thHigh, float nnratio, orbfe_proj_match* out,
-                                                                uint8_t* __restrict__ takenOut) {
+                                                                const int32_t* __restrict__ qOff, int thHigh, float nnratio, int checkOri,
+                                                                orbfe_proj_match* out, uint8_t* __restrict__ takenOut) {
     extern __shared__ __align__(16) unsigned char pj_raw[];
     PjSmem& s = *reinterpret_cast<PjSmem*>(pj_raw);
     const int tid = threadIdx.x, f = blockIdx.x;
@@ -103,6 +106,7 @@ __global__ void __launch_bounds__(PJ_NT) k_search_by_projection(int maxKp, const
     const uint4* qdesc = reinterpret_cast<const uint4*>(qdescAll) + (size_t)q0 * 2;
     orbfe_proj_match* res = out + q0;
     volatile int* status = &res[0].status; /* stride 7 ints; PJ_PENDING while unresolved */
+    __shared__ int s_rot[32];
 
     if (fr.n > maxKp || fr.n > PJ_MAXKP || fr.n < 0) { /* the caller's promise about the frame size does not hold */
         for (int q = tid; q < nq; q += PJ_NT) {
@@ -186,7 +190,8 @@ __global__ void __launch_bounds__(PJ_NT) k_search_by_projection(int maxKp, const
         for (int q = tid; q < nq; q += PJ_NT) {
             if (status[q * 7] != PJ_PENDING) continue;
             const orbfe_proj_query p = qs[q];
-            if (p.flags & ORBFE_PQ_AFTER_LEFT) res[q].accepted = (q > 0 && status[(q - 1) * 7] == PJ_PENDING) ? 0 : 1;   /* may I look at q-1 in step B? */
+            if (p.flags & (ORBFE_PQ_AFTER_LEFT | ORBFE_PQ_NEEDS_LEFT_WINDOW))
+                res[q].accepted = (q > 0 && status[(q - 1) * 7] == PJ_PENDING) ? 0 : 1;   /* may I look at q-1 in step B? */
             pj_window(fr, s, p, [&](int row, int) {
                 if (takenB[row] & 1) return;
                 if (gateRight) {
@@ -206,17 +211,20 @@ __global__ void __launch_bounds__(PJ_NT) k_search_by_projection(int maxKp, const
         for (int q = tid; q < nq; q += PJ_NT) {
             if (status[q * 7] != PJ_PENDING) continue;
             const orbfe_proj_query p = qs[q];
-            if (p.flags & ORBFE_PQ_AFTER_LEFT) {
+            if (p.flags & (ORBFE_PQ_AFTER_LEFT | ORBFE_PQ_NEEDS_LEFT_WINDOW)) {
                 if (res[q].accepted == 0) { pending++; continue; }
                 res[q].accepted = 0;
-                if (q > 0 && status[(q - 1) * 7] == ORBFE_PS_RATIO_REJECTED && !(qs[q - 1].flags & ORBFE_PQ_RIGHT)) {
-                    status[q * 7] = ORBFE_PS_DROPPED;   /* the `continue` of ORBmatcher.cc:117-118 skips this half too */
+                const int prev = q > 0 && !(qs[q - 1].flags & ORBFE_PQ_RIGHT) ? status[(q - 1) * 7] : -2;
+                if (((p.flags & ORBFE_PQ_AFTER_LEFT) && prev == ORBFE_PS_RATIO_REJECTED) ||        /* `continue` at ORBmatcher.cc:117-118 */
+                    ((p.flags & ORBFE_PQ_NEEDS_LEFT_WINDOW) && prev == ORBFE_PS_EMPTY_WINDOW)) {   /* `continue` at ORBmatcher.cc:2262-2263 */
+                    status[q * 7] = ORBFE_PS_DROPPED;
                     continue;
                 }
             }
             const uint4 qa = __ldg(qdesc + 2 * q), qb = __ldg(qdesc + 2 * q + 1);
-            int bestDist = 256, bestLevel = -1, bestDist2 = 256, bestLevel2 = -1, bestIdx = -1;
+            int bestDist = 256, bestLevel = -1, bestDist2 = 256, bestLevel2 = -1, bestIdx = -1, seen = 0;
             pj_window(fr, s, p, [&](int row, int oct) {
+                seen++;
                 if (takenB[row] & 1) return;
                 if (gateRight) {
                     const float ur = __ldg(fr.uRight + row);
@@ -226,19 +234,21 @@ __global__ void __launch_bounds__(PJ_NT) k_search_by_projection(int maxKp, const
                 if (dist < bestDist) { bestDist2 = bestDist; bestDist = dist; bestLevel2 = bestLevel; bestLevel = oct; bestIdx = row; }
                 else if (dist < bestDist2) { bestLevel2 = oct; bestDist2 = dist; }
             });
-            int st = ORBFE_PS_NO_CANDIDATES;
+            int st = seen ? ORBFE_PS_NO_CANDIDATES : ORBFE_PS_EMPTY_WINDOW;
             bool blocked = false;
             int partnerRow = -1;
             if (bestIdx >= 0) {
+                const bool bestOnly = (p.flags & ORBFE_PQ_BEST_ONLY) != 0;
                 st = bestDist > thHigh ? ORBFE_PS_OVER_THRESHOLD
-                     : (bestLevel == bestLevel2 && (float)bestDist > nnratio * (float)bestDist2) ? ORBFE_PS_RATIO_REJECTED : ORBFE_PS_ACCEPTED;
+                     : (!bestOnly && bestLevel == bestLevel2 && (float)bestDist > nnratio * (float)bestDist2) ? ORBFE_PS_RATIO_REJECTED : ORBFE_PS_ACCEPTED;
+                const int reach = bestDist2;   /* candidates above it cannot change any reported field */
                 pj_window(fr, s, p, [&](int row, int) {
                     if (blocked || (takenB[row] & 1)) return;
                     if (gateRight) {
                         const float ur = __ldg(fr.uRight + row);
                         if (ur > 0 && fabsf(p.xr - ur) > p.radius) return;
                     }
-                    if (s.owner[row] < q && pj_ham(qa, qb, __ldg(fr.desc + 2 * row), __ldg(fr.desc + 2 * row + 1)) <= bestDist2) blocked = true;
+                    if (s.owner[row] < q && pj_ham(qa, qb, __ldg(fr.desc + 2 * row), __ldg(fr.desc + 2 * row + 1)) <= reach) blocked = true;
                 });
                 if (st == ORBFE_PS_ACCEPTED && stereoRig) {
                     const int pt = __ldg(fr.partner + bestIdx);
@@ -257,6 +267,49 @@ __global__ void __launch_bounds__(PJ_NT) k_search_by_projection(int maxKp, const
         }
         if (__syncthreads_count(pending) == 0) break;
     }
+    /* ---- rotation consistency (ORBmatcher.cc:2305-2322, 2391-2412): histogram of kpLF.angle - kpCF.angle over the matches ---- */
+    if (checkOri) {
+        const float factor = 1.0f / 30.0f;   /* 1.0f/HISTO_LENGTH */
+        if (tid < 32) s_rot[tid] = 0;
+        __syncthreads();
+        for (int q = tid; q < nq; q += PJ_NT) {
+            if (status[q * 7] != ORBFE_PS_ACCEPTED) continue;
+            float rot = qs[q].angle - __ldg(&fr.kps[res[q].best_idx].angle);
+            if (rot < 0.0f) rot += 360.0f;
+            int bin = (int)roundf(rot * factor);
+            if (bin == 30) bin = 0;
+            if (bin >= 0 && bin < 30) atomicAdd(&s_rot[bin], 1);
+        }
+        __syncthreads();
+        if (tid == 0) {   /* ComputeThreeMaxima (ORBmatcher.cc:2545-2586) */
+            int ind1 = -1, ind2 = -1, ind3 = -1, max1 = 0, max2 = 0, max3 = 0;
+            for (int i = 0; i < 30; i++) {
+                const int c = s_rot[i];
+                if (c > max1) { max3 = max2; max2 = max1; max1 = c; ind3 = ind2; ind2 = ind1; ind1 = i; }
+                else if (c > max2) { max3 = max2; max2 = c; ind3 = ind2; ind2 = i; }
+                else if (c > max3) { max3 = c; ind3 = i; }
+            }
+            if ((float)max2 < 0.1f * (float)max1) { ind2 = -1; ind3 = -1; }
+            else if ((float)max3 < 0.1f * (float)max1) { ind3 = -1; }
+            s_rot[30] = ind1; s_rot[31] = (ind2 & 0xFF) | ((ind3 & 0xFF) << 8);
+        }
+        __syncthreads();
+        const int ind1 = s_rot[30], ind2 = (int)(signed char)(s_rot[31] & 0xFF), ind3 = (int)(signed char)((s_rot[31] >> 8) & 0xFF);
+        for (int q = tid; q < nq; q += PJ_NT) {
+            if (status[q * 7] != ORBFE_PS_ACCEPTED) continue;
+            const int row = res[q].best_idx;
+            float rot = qs[q].angle - __ldg(&fr.kps[row].angle);
+            if (rot < 0.0f) rot += 360.0f;
+            int bin = (int)roundf(rot * factor);
+            if (bin == 30) bin = 0;
+            if (bin >= 0 && bin < 30 && bin != ind1 && bin != ind2 && bin != ind3) {
+                res[q].accepted = 0;
+                status[q * 7] = ORBFE_PS_ROTATION;
+                takenB[row] = 0;                 /* mvpMapPoints[row] = NULL */
+            }
+        }
+        __syncthreads();
+    }
     if (takenOut)
         for (int i = tid; i < fr.n; i += PJ_NT) takenOut[k0 + i] = takenB[i] ? 1 : 0;
 }
@@ -266,8 +319,8 @@ extern "C" {
 int orbfe_search_by_projection_device(int device, int nframes, int max_keypoints, const orbfe_keypoint* d_kps, const uint8_t* d_desc,
                                       const int32_t* d_kp_offsets, const int32_t* d_n_left, const float* d_u_right, const int32_t* d_partner,
                                       const uint8_t* d_taken_in, const orbfe_frame_grid* d_grids, const orbfe_proj_query* d_queries,
-                                      const uint8_t* d_qdesc, const int32_t* d_q_offsets, int th_high, float nnratio, orbfe_proj_match* d_out,
-                                      uint8_t* d_taken_out, void* stream) {
+                                      const uint8_t* d_qdesc, const int32_t* d_q_offsets, int th_high, float nnratio, int check_orientation,
+                                      orbfe_proj_match* d_out, uint8_t* d_taken_out, void* stream) {
     if (nframes < 1 || !d_kps || !d_desc || !d_kp_offsets || !d_grids || !d_queries || !d_qdesc || !d_q_offsets || !d_out) { orbfe_set_error("bad argument"); return ORBFE_E_INVALID; }
     if (max_keypoints < 0 || max_keypoints > PJ_MAXKP) { orbfe_set_error("at most %d keypoints per frame (both cameras together)", PJ_MAXKP); return ORBFE_E_CAPACITY; }
     if (((uintptr_t)d_desc | (uintptr_t)d_qdesc) & 15) { orbfe_set_error("descriptor arrays must be 16-byte aligned"); return ORBFE_E_INVALID; }
@@ -279,14 +332,14 @@ int orbfe_search_by_projection_device(int device, int nframes, int max_keypoints
     }
     k_search_by_projection<<<nframes, PJ_NT, sizeof(PjSmem), (cudaStream_t)stream>>>(max_keypoints, d_kps, d_desc, d_kp_offsets, d_n_left, d_u_right, d_partner,
                                                                                     d_taken_in, d_grids, d_queries, d_qdesc, d_q_offsets, th_high, nnratio,
-                                                                                    d_out, d_taken_out);
+                                                                                    check_orientation ? 1 : 0, d_out, d_taken_out);
     ORBFE_CUDA(cudaGetLastError());
     return ORBFE_OK;
 }
 
 int orbfe_search_by_projection(int device, const orbfe_keypoint* kps, const uint8_t* desc, int n, int n_left, const float* u_right, const int32_t* partner,
                                uint8_t* taken, const orbfe_frame_grid* grid, const orbfe_proj_query* queries, const uint8_t* qdesc, int nq, int th_high,
-                               float nnratio, orbfe_proj_match* out, int* nmatches) {
+                               float nnratio, int check_orientation, orbfe_proj_match* out, int* nmatches) {
     if (!kps || !desc || !grid || !queries || !qdesc || !out || n < 0 || nq < 0) { orbfe_set_error("bad argument"); return ORBFE_E_INVALID; }
     if (n > PJ_MAXKP) { orbfe_set_error("at most %d keypoints per frame (both cameras together)", PJ_MAXKP); return ORBFE_E_CAPACITY; }
     if (nmatches) *nmatches = 0;
@@ -324,7 +377,7 @@ int orbfe_search_by_projection(int device, const orbfe_keypoint* kps, const uint
         rc = orbfe_search_by_projection_device(device, 1, PJ_MAXKP, (const orbfe_keypoint*)(d + oKps), d + oDesc, (const int32_t*)(d + oOff),
                                                (const int32_t*)(d + oOff) + 4, u_right ? (const float*)(d + oUr) : nullptr,
                                                partner ? (const int32_t*)(d + oPt) : nullptr, taken ? d + oTk : nullptr, (const orbfe_frame_grid*)(d + oGrid),
-                                               (const orbfe_proj_query*)(d + oQ), d + oQd, (const int32_t*)(d + oOff) + 2, th_high, nnratio,
+                                               (const orbfe_proj_query*)(d + oQ), d + oQd, (const int32_t*)(d + oOff) + 2, th_high, nnratio, check_orientation,
                                                (orbfe_proj_match*)(d + oOut), taken ? d + oTk : nullptr, st);
     if (rc == ORBFE_OK && e == cudaSuccess) e = cudaMemcpyAsync(out, d + oOut, (size_t)nq * sizeof(orbfe_proj_match), cudaMemcpyDeviceToHost, st);
     if (rc == ORBFE_OK && e == cudaSuccess && taken && n > 0) e = cudaMemcpyAsync(taken, d + oTk, (size_t)n, cudaMemcpyDeviceToHost, st);

@@ -1,6 +1,6 @@
 """Host-side mirror of the projection-gated search over the C ABI:
 ORBmatcher::SearchByProjection(Frame&, const vector<MapPoint*>&, th, bFarPoints, thFarPoints)
-(/root/reference/src/ORBmatcher.cc:44-214), with Frame::AssignFeaturesToGrid / GetFeaturesInArea
+(/root/reference/src/ORBmatcher.cc:44-214) and SearchByProjection(CurrentFrame, LastFrame, th, bMono) (:2193-2419), with Frame::AssignFeaturesToGrid / GetFeaturesInArea
 (/root/reference/src/Frame.cc:380-411, 643-709) inside."""
 import ctypes as C
 
@@ -10,11 +10,12 @@ from . import _lib
 from ._lib import KP_DTYPE, check, ptr
 
 PROJ_QUERY_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("radius", "<f4"), ("xr", "<f4"), ("min_level", "<i4"), ("max_level", "<i4"),
-                             ("flags", "<i4")])
+                             ("flags", "<i4"), ("angle", "<f4")])
 PROJ_MATCH_DTYPE = np.dtype([("best_idx", "<i4"), ("best_dist", "<i4"), ("best_level", "<i4"), ("second_dist", "<i4"),
                              ("second_level", "<i4"), ("accepted", "<i4"), ("status", "<i4")])
-PQ_RIGHT, PQ_BLOCKS, PQ_SKIP, PQ_AFTER_LEFT = 1, 2, 4, 8
-PS_NO_CANDIDATES, PS_ACCEPTED, PS_OVER_THRESHOLD, PS_RATIO_REJECTED, PS_SKIPPED, PS_CAPACITY, PS_DROPPED = range(7)
+PQ_RIGHT, PQ_BLOCKS, PQ_SKIP, PQ_AFTER_LEFT, PQ_BEST_ONLY, PQ_NEEDS_LEFT_WINDOW = 1, 2, 4, 8, 16, 32
+(PS_NO_CANDIDATES, PS_ACCEPTED, PS_OVER_THRESHOLD, PS_RATIO_REJECTED, PS_SKIPPED, PS_CAPACITY, PS_DROPPED, PS_ROTATION,
+ PS_EMPTY_WINDOW) = range(9)
 TH_HIGH = 100   # ORBmatcher.cc:36
 FRAME_GRID_COLS, FRAME_GRID_ROWS = 64, 48   # include/Frame.h:37-38
 
@@ -31,7 +32,7 @@ def frame_grid(min_x, max_x, min_y, max_y):
 
 
 def search_by_projection(kps, desc, queries, qdesc, grid, n_left=-1, u_right=None, partner=None, taken=None, th_high=TH_HIGH, nnratio=0.8,
-                         device=0):
+                         check_orientation=False, device=0):
     """One frame, host arrays.  Returns (matches[PROJ_MATCH_DTYPE], taken_after u8[n], nmatches)."""
     kps = np.ascontiguousarray(kps, KP_DTYPE)
     desc = np.ascontiguousarray(desc, np.uint8)
@@ -47,15 +48,16 @@ def search_by_projection(kps, desc, queries, qdesc, grid, n_left=-1, u_right=Non
     nm = C.c_int(0)
     check(_lib.lib().orbfe_search_by_projection(device, ptr(kps), ptr(desc), n, n_left, ptr(ur) if ur is not None else None,
                                                 ptr(pt) if pt is not None else None, ptr(tk), ptr(grid), ptr(queries), ptr(qdesc), nq,
-                                                th_high, C.c_float(nnratio), ptr(out), C.byref(nm)))
+                                                th_high, C.c_float(nnratio), int(check_orientation), ptr(out), C.byref(nm)))
     return out, tk, nm.value
 
 
 def search_by_projection_device(nframes, max_keypoints, d_kps, d_desc, d_kp_offsets, d_grids, d_queries, d_qdesc, d_q_offsets, d_out,
                                 d_n_left=None, d_u_right=None, d_partner=None, d_taken_in=None, d_taken_out=None, th_high=TH_HIGH,
-                                nnratio=0.8, device=0, stream=None):
+                                nnratio=0.8, check_orientation=False, device=0, stream=None):
     """A batch of frames, device pointers (ints), asynchronous on `stream`."""
     vp = lambda p: C.c_void_p(p) if p else None  # noqa: E731
     check(_lib.lib().orbfe_search_by_projection_device(device, nframes, max_keypoints, vp(d_kps), vp(d_desc), vp(d_kp_offsets), vp(d_n_left),
                                                        vp(d_u_right), vp(d_partner), vp(d_taken_in), vp(d_grids), vp(d_queries), vp(d_qdesc),
-                                                       vp(d_q_offsets), th_high, C.c_float(nnratio), vp(d_out), vp(d_taken_out), vp(stream)))
+                                                       vp(d_q_offsets), th_high, C.c_float(nnratio), int(check_orientation), vp(d_out), vp(d_taken_out),
+                                                       vp(stream)))

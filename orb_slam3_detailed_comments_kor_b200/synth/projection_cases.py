@@ -3,8 +3,9 @@ A case is a dict of arrays in the layouts of include/orbfe.h (orbfe_keypoint, or
 import numpy as np
 
 KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"), ("response", "<f4"), ("octave", "<i4"), ("class_id", "<i4")])
-PROJ_QUERY_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("radius", "<f4"), ("xr", "<f4"), ("min_level", "<i4"), ("max_level", "<i4"), ("flags", "<i4")])
-PQ_RIGHT, PQ_BLOCKS, PQ_SKIP, PQ_AFTER_LEFT = 1, 2, 4, 8
+PROJ_QUERY_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("radius", "<f4"), ("xr", "<f4"), ("min_level", "<i4"), ("max_level", "<i4"), ("flags", "<i4"),
+                             ("angle", "<f4")])
+PQ_RIGHT, PQ_BLOCKS, PQ_SKIP, PQ_AFTER_LEFT, PQ_BEST_ONLY, PQ_NEEDS_LEFT_WINDOW = 1, 2, 4, 8, 16, 32
 
 
 def _flip(rng, d, k):
@@ -14,9 +15,11 @@ def _flip(rng, d, k):
     return d
 
 
-def make_case(seed, n=600, nq=700, W=752, H=480, th=1.0, fisheye=False, stereo_gate=False, crowd=0.0):
+def make_case(seed, n=600, nq=700, W=752, H=480, th=1.0, fisheye=False, stereo_gate=False, crowd=0.0, last_frame=None):
     """crowd: fraction of the map points aimed at a small set of keypoints (long chains of map points competing for the same
-    keypoints); th: the search-window factor of SearchByProjection."""
+    keypoints); th: the search-window factor of SearchByProjection.  last_frame: None = the SearchLocalPoints overload;
+    "still" / "forward" / "backward" = SearchByProjection(CurrentFrame, LastFrame, th, bMono) with the level range of that
+    motion (src/ORBmatcher.cc:2253-2258), best-only acceptance and the rotation check (case["check_orientation"] = 1)."""
     rng = np.random.RandomState(seed)
     f32 = np.float32
     kps = np.zeros(n, KP_DTYPE)
@@ -30,6 +33,7 @@ def make_case(seed, n=600, nq=700, W=752, H=480, th=1.0, fisheye=False, stereo_g
     kps["octave"] = np.minimum(rng.geometric(0.3, n) - 1, 7)
     kps["size"] = 31
     kps["class_id"] = -1
+    kps["angle"] = rng.uniform(0, 360, n).astype(f32)
     desc = rng.randint(0, 256, (n, 32)).astype(np.uint8)
     desc[dst[: n // 8]] = desc[src[: n // 8]]                   # exact descriptor duplicates next to each other: distance ties
     n_left = -1
@@ -37,7 +41,9 @@ def make_case(seed, n=600, nq=700, W=752, H=480, th=1.0, fisheye=False, stereo_g
         n_left = n // 2 + 7
     case = {"kps": kps, "desc": desc, "n_left": np.array([n_left], np.int32),
             "grid": np.array([0, 0, f32(64) / f32(W), f32(48) / f32(H)], f32), "th_high": np.array([100], np.int32),
-            "nnratio": np.array([0.8], f32), "taken": (rng.uniform(size=n) < 0.08).astype(np.uint8)}
+            "nnratio": np.array([0.8], f32), "taken": (rng.uniform(size=n) < 0.08).astype(np.uint8),
+            "check_orientation": np.array([1 if last_frame else 0], np.int32)}
+    turn = f32(rng.uniform(-40, 40))                          # camera roll between the two frames (last_frame cases)
     if stereo_gate:
         ur = kps["x"] - rng.uniform(1, 40, n).astype(f32)
         ur[rng.uniform(size=n) < 0.4] = -1
@@ -79,18 +85,26 @@ def make_case(seed, n=600, nq=700, W=752, H=480, th=1.0, fisheye=False, stereo_g
         minl, maxl = lvl - 1, lvl
         if rng.uniform() < 0.03:
             minl, maxl = 0, -1                                  # bCheckLevels == false
+        ang = f32(0)
+        if last_frame:
+            flags |= PQ_BEST_ONLY
+            minl, maxl = {"still": (lvl - 1, lvl + 1), "forward": (lvl, -1), "backward": (0, lvl)}[last_frame]
+            # most matches turn by the camera roll (one or two histogram bins); the rest are scattered and get filtered
+            ang = f32((kps["angle"][t] if t >= 0 else 0) + (turn + rng.uniform(-4, 4) if rng.uniform() < 0.8 else rng.uniform(0, 360)))
+            ang = f32(ang % 360)
         if fisheye:
             right_target = t >= n_left
             # left-camera half, then (for most points) the right-camera half of the same map point
-            q.append((x, y, r, xr, minl, maxl, flags | (PQ_RIGHT if right_target and rng.uniform() < 0.5 else 0)))
+            q.append((x, y, r, xr, minl, maxl, flags | (PQ_RIGHT if right_target and rng.uniform() < 0.5 else 0), ang))
             qd.append(d)
             count += 1
             if not (q[-1][6] & PQ_RIGHT) and rng.uniform() < 0.7:
-                q.append((f32(x + rng.uniform(-2, 2)), f32(y + rng.uniform(-2, 2)), r, xr, minl, maxl, flags | PQ_RIGHT | PQ_AFTER_LEFT))
+                dep = PQ_NEEDS_LEFT_WINDOW if last_frame else PQ_AFTER_LEFT
+                q.append((f32(x + rng.uniform(-2, 2)), f32(y + rng.uniform(-2, 2)), r, xr, minl, maxl, flags | PQ_RIGHT | dep, ang))
                 qd.append(d)
                 count += 1
         else:
-            q.append((x, y, r, xr, minl, maxl, flags))
+            q.append((x, y, r, xr, minl, maxl, flags, ang))
             qd.append(d)
             count += 1
     case["queries"] = np.array(q, PROJ_QUERY_DTYPE)
@@ -104,4 +118,7 @@ CASES = {
     "stereo_gate": dict(seed=12, n=800, nq=900, stereo_gate=True),
     "wide": dict(seed=13, n=500, nq=600, th=3.0, crowd=0.5),
     "fisheye": dict(seed=14, n=900, nq=800, fisheye=True, th=1.5, crowd=0.3),
+    "last_still": dict(seed=15, n=800, nq=700, th=7.0, stereo_gate=True, crowd=0.2, last_frame="still"),
+    "last_forward": dict(seed=16, n=700, nq=600, th=15.0, crowd=0.4, last_frame="forward"),
+    "last_backward_fisheye": dict(seed=17, n=900, nq=800, th=7.0, fisheye=True, crowd=0.3, last_frame="backward"),
 }

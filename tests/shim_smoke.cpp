@@ -29,7 +29,7 @@ int main(int argc, char** argv) {
     for (size_t i = 0; i < kL.size(); i++) {
         pq[i].x = kL[i].pt.x + 0.5f; pq[i].y = kL[i].pt.y - 0.5f;
         pq[i].radius = 4.0f * left.GetScaleFactors()[kL[i].octave];
-        pq[i].xr = uR[i]; pq[i].min_level = kL[i].octave - 1; pq[i].max_level = kL[i].octave; pq[i].flags = ORBFE_PQ_BLOCKS;
+        pq[i].xr = uR[i]; pq[i].min_level = kL[i].octave - 1; pq[i].max_level = kL[i].octave; pq[i].flags = ORBFE_PQ_BLOCKS; pq[i].angle = 0.f;
     }
     std::vector<unsigned char> taken;
     std::vector<orbfe_proj_match> pm;

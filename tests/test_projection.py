@@ -26,11 +26,13 @@ def _golden_case(g, name):
 
 def _run(fn, c, **kw):
     return fn(c["kps"], c["desc"], c["queries"], c["qdesc"], c["grid"], n_left=int(c["n_left"][0]), u_right=c.get("u_right"),
-              partner=c.get("partner"), taken=c["taken"], th_high=int(c["th_high"][0]), nnratio=float(c["nnratio"][0]), **kw)
+              partner=c.get("partner"), taken=c["taken"], th_high=int(c["th_high"][0]), nnratio=float(c["nnratio"][0]),
+              check_orientation=bool(c["check_orientation"][0]), **kw)
 
 
 def test_oracle_matches_python_restatement():
     g = np.load(GOLD)
+    seen_status = set()
     for name, kw in PC.CASES.items():
         c = _golden_case(g, name)
         fresh = PC.make_case(**kw)
@@ -39,7 +41,9 @@ def test_oracle_matches_python_restatement():
         out, taken, nm = _run(O.search_by_projection, c)
         assert np.array_equal(_as_matrix(out), c["expect"]), name
         assert np.array_equal(taken, c["taken_after"]) and nm == int(c["nmatches"][0]), name
-        assert (out["status"] == 1).sum() > 100 and (out["status"] == 3).sum() > 0
+        assert (out["status"] == 1).sum() > 100
+        seen_status.update(out["status"].tolist())
+    assert seen_status >= {0, 1, 2, 3, 4, 6, 7, 8}, seen_status      # every outcome occurs somewhere in the goldens
 
 
 def test_oracle_known_answers():
@@ -71,12 +75,16 @@ def test_gpu_search_matches_oracle_and_goldens():
     for name in PC.CASES:
         c = _golden_case(g, name)
         out, taken, nm = _run(P.search_by_projection, c)
-        assert np.array_equal(_as_matrix(out), c["expect"]), name
+        bad = np.nonzero((_as_matrix(out) != c["expect"]).any(1))[0]
+        assert bad.size == 0, (name, bad[:5], _as_matrix(out)[bad[:3]], c["expect"][bad[:3]])
         assert np.array_equal(taken, c["taken_after"]) and nm == int(c["nmatches"][0]), name
     # larger and harder: the per-frame capacity, wide windows and crowds (long chains of map points after the same keypoints)
     for kw in (dict(seed=21, n=4096, nq=6000, th=1.0), dict(seed=22, n=3000, nq=5000, th=5.0, crowd=0.6, stereo_gate=True),
                dict(seed=23, n=2600, nq=4000, th=3.0, crowd=0.8, fisheye=True), dict(seed=24, n=40, nq=900, th=15.0, crowd=1.0),
-               dict(seed=25, n=1, nq=5), dict(seed=26, n=1500, nq=1, th=2.0)):
+               dict(seed=25, n=1, nq=5), dict(seed=26, n=1500, nq=1, th=2.0),
+               dict(seed=29, n=2400, nq=3000, th=7.0, stereo_gate=True, crowd=0.3, last_frame="still"),
+               dict(seed=30, n=3000, nq=3500, th=15.0, fisheye=True, crowd=0.5, last_frame="forward"),
+               dict(seed=31, n=60, nq=800, th=15.0, crowd=1.0, last_frame="backward")):
         c = PC.make_case(**kw)
         want, wtaken, wnm = _run(O.search_by_projection, c)
         out, taken, nm = _run(P.search_by_projection, c)
@@ -97,7 +105,8 @@ def test_gpu_search_matches_oracle_and_goldens():
 def test_gpu_search_batch_device():
     import torch
     from orb_slam3_detailed_comments_kor_b200 import projection as P
-    cases = [PC.make_case(seed=40 + i, n=900 + 150 * i, nq=1100 + 100 * i, th=1.0 + 0.5 * (i % 3), crowd=0.2 * (i % 3), stereo_gate=True)
+    cases = [PC.make_case(seed=40 + i, n=900 + 150 * i, nq=1100 + 100 * i, th=1.0 + 0.5 * (i % 3), crowd=0.2 * (i % 3), stereo_gate=True,
+                          last_frame="still")
              for i in range(7)]
     cases[3]["kps"] = np.concatenate([cases[3]["kps"]] * 3)[:2000]     # frame 3 breaks the max_keypoints promise below
     cases[3]["desc"] = np.concatenate([cases[3]["desc"]] * 3)[:2000]
@@ -116,7 +125,7 @@ def test_gpu_search_batch_device():
         d_tko = torch.zeros(int(koff[-1]), dtype=torch.uint8, device="cuda")
         P.search_by_projection_device(len(cases), 1999, d_kps.data_ptr(), d_desc.data_ptr(), d_koff.data_ptr(), d_grid.data_ptr(), d_q.data_ptr(),
                                       d_qd.data_ptr(), d_qoff.data_ptr(), d_out.data_ptr(), d_u_right=d_ur.data_ptr(), d_taken_in=d_tk.data_ptr(),
-                                      d_taken_out=d_tko.data_ptr(), stream=st.cuda_stream)
+                                      d_taken_out=d_tko.data_ptr(), check_orientation=True, stream=st.cuda_stream)
         out = d_out.cpu().numpy().view(P.PROJ_MATCH_DTYPE)
         tko = d_tko.cpu().numpy()
     st.synchronize()

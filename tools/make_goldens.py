@@ -384,6 +384,8 @@ def py_search_by_projection(c):
     ur, partner = c.get("u_right"), c.get("partner")
     taken = c["taken"].astype(bool).copy()
     th_high, ratio = int(c["th_high"][0]), f32(c["nnratio"][0])
+    check_ori = int(c["check_orientation"][0]) != 0
+    rot_hist = [[] for _ in range(30)]
     popc = np.array([bin(i).count("1") for i in range(256)], np.int32)
     cells = {}
     for i in range(n):
@@ -395,12 +397,14 @@ def py_search_by_projection(c):
     res = np.zeros((len(q), 7), np.int32)
     nmatches = 0
     skip_right_half = False
+    left_window_empty = False
     for k in range(len(q)):
         x, y, r, xr = f32(q["x"][k]), f32(q["y"][k]), f32(q["radius"][k]), f32(q["xr"][k])
         minl, maxl, flags = int(q["min_level"][k]), int(q["max_level"][k]), int(q["flags"][k])
         res[k] = (-1, 256, -1, 256, -1, 0, 0)
-        drop = bool(flags & 8) and skip_right_half
+        drop = (bool(flags & 8) and skip_right_half) or (bool(flags & 32) and left_window_empty)
         skip_right_half = False
+        left_window_empty = False
         if flags & 4:
             res[k, 6] = 4
             continue
@@ -422,6 +426,10 @@ def py_search_by_projection(c):
                             continue
                         if abs(f32(kps["x"][i]) - x) < r and abs(f32(kps["y"][i]) - y) < r:
                             cand.append(i)
+        if not cand:
+            res[k, 6] = 8
+            left_window_empty = not side
+            continue
         best, blvl, best2, blvl2, bidx = 256, -1, 256, -1, -1
         for i in cand:
             if taken[i]:
@@ -440,7 +448,7 @@ def py_search_by_projection(c):
         if best > th_high:
             res[k, 6] = 2
             continue
-        if blvl == blvl2 and f32(best) > ratio * f32(best2):
+        if not (flags & 16) and blvl == blvl2 and f32(best) > ratio * f32(best2):
             res[k, 6] = 3
             skip_right_half = not side
             continue
@@ -452,6 +460,35 @@ def py_search_by_projection(c):
             nmatches += 1
             if flags & 2:
                 taken[partner[bidx]] = True
+        if check_ori:
+            rot = f32(q["angle"][k]) - f32(kps["angle"][bidx])
+            if rot < 0:
+                rot = f32(rot + f32(360))
+            v = f32(rot * f32(f32(1) / f32(30)))
+            b = int(math.floor(abs(float(v)) + 0.5))              # C round(): half away from zero (v >= 0 here)
+            if b == 30:
+                b = 0
+            rot_hist[b].append(k)
+    if check_ori:
+        sizes = [len(h) for h in rot_hist]
+        ind, mx = [-1, -1, -1], [0, 0, 0]
+        for i, sz in enumerate(sizes):                            # ComputeThreeMaxima
+            if sz > mx[0]:
+                mx = [sz, mx[0], mx[1]]; ind = [i, ind[0], ind[1]]
+            elif sz > mx[1]:
+                mx = [mx[0], sz, mx[1]]; ind = [ind[0], i, ind[1]]
+            elif sz > mx[2]:
+                mx[2] = sz; ind[2] = i
+        if f32(mx[1]) < f32(0.1) * f32(mx[0]):
+            ind[1] = ind[2] = -1
+        elif f32(mx[2]) < f32(0.1) * f32(mx[0]):
+            ind[2] = -1
+        for i in range(30):
+            if i not in ind:
+                for k in rot_hist[i]:
+                    res[k, 5], res[k, 6] = 0, 7
+                    taken[res[k, 0]] = False
+                    nmatches -= 2 if (nleft >= 0 and partner is not None and partner[res[k, 0]] >= 0) else 1
     return res, taken.astype(np.uint8), nmatches
 
 
