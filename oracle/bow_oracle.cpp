@@ -122,4 +122,77 @@ int orc_bow_transform(const orc_vocabulary* voc, const uint8_t* features, int n,
     return 0;
 }
 
+/* ORBmatcher::SearchByBoW(KeyFrame* pKF, Frame &F, vector<MapPoint*>&), src/ORBmatcher.cc:269-470, the F.Nleft == -1 path, with
+ * ComputeThreeMaxima (:2545-2586).  The feature vectors are the (nodes, starts, feats) arrays of orc_bow_transform.
+ * match_f[i] = keyframe row whose map point lands in vpMapPointMatches[i], or -1; kf_out (optional): per keyframe row the scan's
+ * best1/best2/idx and accepted (1 kept, 2 removed by the rotation histogram).  Returns nmatches. */
+int orc_search_by_bow(const uint8_t* desc_kf, const orc_keypoint* kps_kf, int n_kf, const int32_t* nodes_kf, const int32_t* starts_kf, const int32_t* feats_kf,
+                      int nfv_kf, const uint8_t* has_map_point, const uint8_t* desc_f, const orc_keypoint* kps_f, int n_f, const int32_t* nodes_f,
+                      const int32_t* starts_f, const int32_t* feats_f, int nfv_f, int th_low, float nnratio, int check_orientation, int32_t* match_f,
+                      orc_match* kf_out) {
+    const int HISTO_LENGTH = 30;
+    for (int i = 0; i < n_f; i++) match_f[i] = -1;
+    if (kf_out) for (int i = 0; i < n_kf; i++) { kf_out[i].best1 = 256; kf_out[i].best2 = 256; kf_out[i].idx = -1; kf_out[i].accepted = 0; }
+    int nmatches = 0;
+    std::vector<int> rotHist[HISTO_LENGTH];
+    const float factor = 1.0f / HISTO_LENGTH;
+    int KFit = 0, Fit = 0;
+    while (KFit != nfv_kf && Fit != nfv_f) {
+        if (nodes_kf[KFit] == nodes_f[Fit]) {
+            for (int iKF = starts_kf[KFit]; iKF < starts_kf[KFit + 1]; iKF++) {
+                const int realIdxKF = feats_kf[iKF];
+                if (has_map_point && !has_map_point[realIdxKF]) continue;
+                const uint8_t* dKF = desc_kf + (size_t)realIdxKF * 32;
+                int bestDist1 = 256, bestIdxF = -1, bestDist2 = 256;
+                for (int iF = starts_f[Fit]; iF < starts_f[Fit + 1]; iF++) {
+                    const int realIdxF = feats_f[iF];
+                    if (match_f[realIdxF] >= 0) continue;
+                    const int dist = orc_descriptor_distance(dKF, desc_f + (size_t)realIdxF * 32);
+                    if (dist < bestDist1) { bestDist2 = bestDist1; bestDist1 = dist; bestIdxF = realIdxF; }
+                    else if (dist < bestDist2) { bestDist2 = dist; }
+                }
+                bool ok = false;
+                if (bestDist1 <= th_low && static_cast<float>(bestDist1) < nnratio * static_cast<float>(bestDist2)) {
+                    ok = true;
+                    match_f[bestIdxF] = realIdxKF;
+                    if (check_orientation) {
+                        float rot = kps_kf[realIdxKF].angle - kps_f[bestIdxF].angle;
+                        if (rot < 0.0) rot += 360.0f;
+                        int bin = (int)std::round(rot * factor);
+                        if (bin == HISTO_LENGTH) bin = 0;
+                        if (bin >= 0 && bin < HISTO_LENGTH) rotHist[bin].push_back(bestIdxF);
+                    }
+                    nmatches++;
+                }
+                if (kf_out) { kf_out[realIdxKF].best1 = bestDist1; kf_out[realIdxKF].best2 = bestDist2; kf_out[realIdxKF].idx = bestIdxF; kf_out[realIdxKF].accepted = ok; }
+            }
+            KFit++; Fit++;
+        } else if (nodes_kf[KFit] < nodes_f[Fit]) {
+            while (KFit != nfv_kf && nodes_kf[KFit] < nodes_f[Fit]) KFit++;   /* lower_bound */
+        } else {
+            while (Fit != nfv_f && nodes_f[Fit] < nodes_kf[KFit]) Fit++;
+        }
+    }
+    if (check_orientation) {
+        int ind1 = -1, ind2 = -1, ind3 = -1, max1 = 0, max2 = 0, max3 = 0;
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            const int c = (int)rotHist[i].size();
+            if (c > max1) { max3 = max2; max2 = max1; max1 = c; ind3 = ind2; ind2 = ind1; ind1 = i; }
+            else if (c > max2) { max3 = max2; max2 = c; ind3 = ind2; ind2 = i; }
+            else if (c > max3) { max3 = c; ind3 = i; }
+        }
+        if (max2 < 0.1f * (float)max1) { ind2 = -1; ind3 = -1; }
+        else if (max3 < 0.1f * (float)max1) { ind3 = -1; }
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            if (i == ind1 || i == ind2 || i == ind3) continue;
+            for (int idxF : rotHist[i]) {
+                if (kf_out) kf_out[match_f[idxF]].accepted = 2;
+                match_f[idxF] = -1;
+                nmatches--;
+            }
+        }
+    }
+    return nmatches;
+}
+
 }  /* extern "C" */

@@ -67,6 +67,8 @@ def lib():
     L.orc_vocabulary_destroy.argtypes = [vp]
     L.orc_vocabulary_words.argtypes = [vp]
     L.orc_bow_transform.argtypes = [vp, vp, C.c_int, C.c_int, vp, vp, vp, vp, vp, vp, vp, vp, vp]
+    L.orc_search_by_bow.argtypes = [vp, vp, C.c_int, vp, vp, vp, C.c_int, vp, vp, vp, C.c_int, vp, vp, vp, C.c_int, C.c_int, C.c_float, C.c_int, vp, vp]
+    L.orc_search_by_bow.restype = C.c_int
     L.orc_distinctive_descriptors.argtypes = [vp, vp, C.c_int, vp, vp]
     L.orc_search_by_projection.argtypes = [vp, vp, C.c_int, C.c_int, vp, vp, vp, vp, vp, vp, C.c_int, C.c_int, C.c_float, C.c_int, vp]
     L.orc_search_by_projection.restype = C.c_int
@@ -257,6 +259,30 @@ class OracleVocabulary:
         nb, nf = nb.value, nf.value
         return {"word_ids": wid, "node_ids": nid, "bow_words": bw[:nb].copy(), "bow_values": bv[:nb].copy(),
                 "feat_vec": {int(fn[e]): ff[fs[e]:fs[e + 1]].copy() for e in range(nf)}}
+
+
+def _fv_arrays(feat_vec):
+    """{node: feature rows} (key order) -> (nodes, starts, feats) int32 arrays"""
+    nodes = np.array(list(feat_vec.keys()), np.int32)
+    lens = [len(v) for v in feat_vec.values()]
+    starts = np.concatenate([[0], np.cumsum(lens)]).astype(np.int32)
+    feats = np.concatenate([np.asarray(v, np.int32) for v in feat_vec.values()]).astype(np.int32) if lens else np.zeros(0, np.int32)
+    return nodes, starts, feats
+
+
+def search_by_bow(desc_kf, kps_kf, fv_kf, has_map_point, desc_f, kps_f, fv_f, th_low=50, nnratio=0.7, check_orientation=True):
+    """ORBmatcher::SearchByBoW(pKF, F, vpMapPointMatches); fv_* = {node: rows} dicts.  Returns (match_f, kf_out, nmatches)."""
+    desc_kf = np.ascontiguousarray(desc_kf, np.uint8); desc_f = np.ascontiguousarray(desc_f, np.uint8)
+    kps_kf = np.ascontiguousarray(kps_kf, KP_DTYPE); kps_f = np.ascontiguousarray(kps_f, KP_DTYPE)
+    na, sa, fa = _fv_arrays(fv_kf)
+    nb, sb, fb = _fv_arrays(fv_f)
+    mp = None if has_map_point is None else np.ascontiguousarray(has_map_point, np.uint8)
+    match_f = np.zeros(max(desc_f.shape[0], 1), np.int32)
+    kf_out = np.zeros(max(desc_kf.shape[0], 1), MATCH_DTYPE)
+    nm = lib().orc_search_by_bow(_ptr(desc_kf), _ptr(kps_kf), desc_kf.shape[0], _ptr(na), _ptr(sa), _ptr(fa), len(na), _ptr(mp) if mp is not None else None,
+                                 _ptr(desc_f), _ptr(kps_f), desc_f.shape[0], _ptr(nb), _ptr(sb), _ptr(fb), len(nb), th_low, nnratio, int(check_orientation),
+                                 _ptr(match_f), _ptr(kf_out))
+    return match_f[:desc_f.shape[0]], kf_out[:desc_kf.shape[0]], nm
 
 
 def distinctive_descriptors(desc, offsets):

@@ -6,7 +6,7 @@ import ctypes as C
 import numpy as np
 
 from . import _lib
-from ._lib import check, ptr
+from ._lib import KP_DTYPE, MATCH_DTYPE, check, ptr
 
 L1_NORM, L2_NORM, CHI_SQUARE, KL, BHATTACHARYYA, DOT_PRODUCT = range(6)   # DBoW2::ScoringType (BowVector.h:48-56)
 TF_IDF, TF, IDF, BINARY = range(4)                                       # DBoW2::WeightingType (BowVector.h:39-45)
@@ -68,3 +68,28 @@ class ORBVocabulary:
 
     def result(self, frame, nfeatures):
         return self._fetch(frame, nfeatures)
+
+
+def _fv_arrays(feat_vec):
+    nodes = np.array(list(feat_vec.keys()), np.int32)
+    lens = [len(v) for v in feat_vec.values()]
+    starts = np.concatenate([[0], np.cumsum(lens)]).astype(np.int32)
+    feats = np.concatenate([np.asarray(v, np.int32) for v in feat_vec.values()]).astype(np.int32) if lens else np.zeros(0, np.int32)
+    return nodes, starts, feats
+
+
+def search_by_bow(desc_kf, kps_kf, fv_kf, has_map_point, desc_f, kps_f, fv_f, th_low=50, nnratio=0.7, check_orientation=True, device=0):
+    """ORBmatcher::SearchByBoW(KeyFrame*, Frame&, vpMapPointMatches) (src/ORBmatcher.cc:269-470) for one pair on the host;
+    fv_* are the feat_vec dicts of ORBVocabulary.transform.  Returns (match_f[nF] keyframe row or -1, kf_out, nmatches)."""
+    desc_kf = np.ascontiguousarray(desc_kf, np.uint8); desc_f = np.ascontiguousarray(desc_f, np.uint8)
+    kps_kf = np.ascontiguousarray(kps_kf, KP_DTYPE); kps_f = np.ascontiguousarray(kps_f, KP_DTYPE)
+    na, sa, fa = _fv_arrays(fv_kf)
+    nb, sb, fb = _fv_arrays(fv_f)
+    mp = None if has_map_point is None else np.ascontiguousarray(has_map_point, np.uint8)
+    match_f = np.zeros(max(desc_f.shape[0], 1), np.int32)
+    kf_out = np.zeros(max(desc_kf.shape[0], 1), MATCH_DTYPE)
+    nm = C.c_int(0)
+    check(_lib.lib().orbfe_search_by_bow(device, ptr(desc_kf), ptr(kps_kf), desc_kf.shape[0], ptr(na), ptr(sa), ptr(fa), len(na),
+                                         ptr(mp) if mp is not None else None, ptr(desc_f), ptr(kps_f), desc_f.shape[0], ptr(nb), ptr(sb), ptr(fb), len(nb),
+                                         th_low, C.c_float(nnratio), int(check_orientation), ptr(match_f), ptr(kf_out), C.byref(nm)))
+    return match_f[:desc_f.shape[0]], kf_out[:desc_kf.shape[0]], nm.value

@@ -13,6 +13,7 @@
  *                    matter); the L1 / L2 norm is accumulated by one thread in ascending word order, exactly the reference's
  *                    loop over the map, then every entry is divided by it. */
 #include <cuda_runtime.h>
+#include <limits.h>
 #include <math.h>
 #include <stdint.h>
 #include <string.h>
@@ -189,6 +190,161 @@ __global__ void __launch_bounds__(BOW_NT) k_bow_assemble(const int* __restrict__
     if (tid == 0) { fvStarts[so + nn] = nv; fvCount[f] = nn; }
 }
 
+/* ------------------------------------------------------------------------------------------------- SearchByBoW */
+/* ORBmatcher::SearchByBoW(KeyFrame* pKF, Frame &F, vector<MapPoint*> &vpMapPointMatches) (/root/reference/src/ORBmatcher.cc:269-470),
+ * the F.Nleft == -1 path: for every vocabulary node present in both feature vectors, every keyframe feature of the node that has
+ * a map point scans the frame's features of the node that are still unmatched (best / second best with the strict `<` rule),
+ * and takes the best one if bestDist1 <= TH_LOW and (float)bestDist1 < mfNNratio * (float)bestDist2; then the rotation histogram
+ * (ComputeThreeMaxima) removes the matches outside the three fullest bins.
+ * One CTA = one (keyframe, frame) pair.  The serial "already matched" rule is reproduced exactly by the speculative rounds of
+ * orbfe_project.cu: a query (one keyframe feature, in feature-vector order) stamps the unmatched frame features of its node,
+ * scans them, and becomes final iff no candidate at or below its second-best distance carries the stamp of an earlier unresolved
+ * query.  Queries of different nodes never share a candidate, so everything but the chains inside a node resolves at once. */
+#define SB_NT 256
+struct SbSmem {
+    int owner[BOW_MAXF];
+    uint32_t range[BOW_MAXF];          /* per query: first | last+1 << 16 of its node's run in the frame's fvFeats (0 = none) */
+    uint32_t taken[BOW_MAXF / 4];      /* per frame feature: bit 0 matched, bit 1 matched as of the next round */
+    uint32_t state[BOW_MAXF / 4];      /* per query: 0 unresolved, 1 resolved */
+    int rot[32];
+};
+
+__global__ void __launch_bounds__(SB_NT) k_search_by_bow(int maxF, const int* __restrict__ pairKf, const int* __restrict__ pairF, const uint4* __restrict__ desc,
+                                                         const orbfe_keypoint* __restrict__ kps, int rowStride, const int* __restrict__ fvNodes,
+                                                         const int* __restrict__ fvStarts, const int* __restrict__ fvFeats, const int* __restrict__ fvCount,
+                                                         const uint8_t* __restrict__ hasMp, int thLow, float nnratio, int checkOri, int* __restrict__ matchF,
+                                                         orbfe_match* __restrict__ kfOut, int* __restrict__ nmatches) {
+    __shared__ SbSmem s;
+    const int tid = threadIdx.x, pr = blockIdx.x;
+    const int a = pairKf[pr], b = pairF[pr];
+    const int* nodesA = fvNodes + (size_t)a * maxF; const int* startsA = fvStarts + (size_t)a * (maxF + 1); const int* featsA = fvFeats + (size_t)a * maxF;
+    const int* nodesB = fvNodes + (size_t)b * maxF; const int* startsB = fvStarts + (size_t)b * (maxF + 1); const int* featsB = fvFeats + (size_t)b * maxF;
+    const int nnA = fvCount[a], nnB = fvCount[b];
+    const int nq = nnA ? startsA[nnA] : 0;                       /* keyframe features that sit in the feature vector */
+    const uint4* descA = desc + (size_t)a * rowStride * 2; const uint4* descB = desc + (size_t)b * rowStride * 2;
+    int* mF = matchF + (size_t)pr * rowStride;
+    orbfe_match* ko = kfOut ? kfOut + (size_t)pr * rowStride : nullptr;
+    uint8_t* takenB = reinterpret_cast<uint8_t*>(s.taken);
+    uint8_t* stateB = reinterpret_cast<uint8_t*>(s.state);
+    for (int i = tid; i < rowStride; i += SB_NT) { mF[i] = -1; if (ko) { orbfe_match m; m.best1 = 256; m.best2 = 256; m.idx = -1; m.accepted = 0; ko[i] = m; } }
+    for (int i = tid; i < BOW_MAXF / 4; i += SB_NT) { s.taken[i] = 0; s.state[i] = 0; }
+    __syncthreads();
+    /* the node of every query, and that node's run in the frame's feature vector (the lockstep walk of :290-420 is a merge join) */
+    for (int e = tid; e < nnA; e += SB_NT) {
+        const int node = nodesA[e];
+        int lo = 0, hi = nnB;
+        while (lo < hi) { const int mid = (lo + hi) >> 1; if (nodesB[mid] < node) lo = mid + 1; else hi = mid; }
+        const uint32_t rg = (lo < nnB && nodesB[lo] == node) ? ((uint32_t)startsB[lo] | ((uint32_t)startsB[lo + 1] << 16)) : 0u;
+        for (int j = startsA[e]; j < startsA[e + 1]; j++) {
+            const int row = featsA[j];
+            const bool live = rg != 0 && (!hasMp || hasMp[(size_t)a * rowStride + row]);   /* pMP && !pMP->isBad() */
+            s.range[j] = live ? rg : 0u;
+            if (!live) stateB[j] = 1;
+        }
+    }
+    __syncthreads();
+    for (;;) {
+        for (int i = tid; i < maxF; i += SB_NT) {
+            s.owner[i] = INT_MAX;
+            if (takenB[i] & 2) takenB[i] = 1;
+        }
+        __syncthreads();
+        for (int q = tid; q < nq; q += SB_NT) {
+            if (stateB[q]) continue;
+            const uint32_t rg = s.range[q];
+            for (int j = rg & 0xFFFF; j < (int)(rg >> 16); j++) {
+                const int row = featsB[j];
+                if (!(takenB[row] & 1)) atomicMin(&s.owner[row], q);
+            }
+        }
+        __syncthreads();
+        int pending = 0;
+        for (int q = tid; q < nq; q += SB_NT) {
+            if (stateB[q]) continue;
+            const uint32_t rg = s.range[q];
+            const int rowA = featsA[q];
+            const uint4 qa = __ldg(descA + 2 * rowA), qb = __ldg(descA + 2 * rowA + 1);
+            int best1 = 256, best2 = 256, bestIdx = -1;
+            for (int j = rg & 0xFFFF; j < (int)(rg >> 16); j++) {
+                const int row = featsB[j];
+                if (takenB[row] & 1) continue;                    /* if(vpMapPointMatches[realIdxF]) continue; */
+                const int dist = bow_ham(qa, qb, __ldg(descB + 2 * row), __ldg(descB + 2 * row + 1));
+                if (dist < best1) { best2 = best1; best1 = dist; bestIdx = row; }
+                else if (dist < best2) best2 = dist;
+            }
+            bool blocked = false;
+            for (int j = rg & 0xFFFF; j < (int)(rg >> 16) && !blocked; j++) {
+                const int row = featsB[j];
+                if ((takenB[row] & 1) || s.owner[row] >= q) continue;
+                if (bow_ham(qa, qb, __ldg(descB + 2 * row), __ldg(descB + 2 * row + 1)) <= best2) blocked = true;
+            }
+            if (blocked) { pending++; continue; }
+            const bool ok = bestIdx >= 0 && best1 <= thLow && (float)best1 < nnratio * (float)best2;
+            stateB[q] = 1;
+            if (ko) { orbfe_match m; m.best1 = best1; m.best2 = best2; m.idx = bestIdx; m.accepted = ok ? 1 : 0; ko[rowA] = m; }
+            if (ok) {
+                mF[bestIdx] = rowA;
+                atomicOr(&s.taken[bestIdx >> 2], 2u << (8 * (bestIdx & 3)));
+            }
+        }
+        if (__syncthreads_count(pending) == 0) break;
+    }
+    /* rotation consistency (:368-384, 440-458) */
+    if (checkOri) {
+        const float factor = 1.0f / 30.0f;
+        const orbfe_keypoint* kA = kps + (size_t)a * rowStride; const orbfe_keypoint* kB = kps + (size_t)b * rowStride;
+        if (tid < 32) s.rot[tid] = 0;
+        __syncthreads();
+        for (int i = tid; i < rowStride; i += SB_NT) {
+            const int ra = mF[i];
+            if (ra < 0) continue;
+            float rot = __ldg(&kA[ra].angle) - __ldg(&kB[i].angle);
+            if (rot < 0.0f) rot += 360.0f;
+            int bin = (int)roundf(rot * factor);
+            if (bin == 30) bin = 0;
+            if (bin >= 0 && bin < 30) atomicAdd(&s.rot[bin], 1);
+        }
+        __syncthreads();
+        if (tid == 0) {
+            int ind1 = -1, ind2 = -1, ind3 = -1, max1 = 0, max2 = 0, max3 = 0;
+            for (int i = 0; i < 30; i++) {
+                const int c = s.rot[i];
+                if (c > max1) { max3 = max2; max2 = max1; max1 = c; ind3 = ind2; ind2 = ind1; ind1 = i; }
+                else if (c > max2) { max3 = max2; max2 = c; ind3 = ind2; ind2 = i; }
+                else if (c > max3) { max3 = c; ind3 = i; }
+            }
+            if ((float)max2 < 0.1f * (float)max1) { ind2 = -1; ind3 = -1; }
+            else if ((float)max3 < 0.1f * (float)max1) { ind3 = -1; }
+            s.rot[30] = ind1; s.rot[31] = (ind2 & 0xFF) | ((ind3 & 0xFF) << 8);
+        }
+        __syncthreads();
+        const int ind1 = s.rot[30], ind2 = (int)(signed char)(s.rot[31] & 0xFF), ind3 = (int)(signed char)((s.rot[31] >> 8) & 0xFF);
+        for (int i = tid; i < rowStride; i += SB_NT) {
+            const int ra = mF[i];
+            if (ra < 0) continue;
+            float rot = __ldg(&kA[ra].angle) - __ldg(&kB[i].angle);
+            if (rot < 0.0f) rot += 360.0f;
+            int bin = (int)roundf(rot * factor);
+            if (bin == 30) bin = 0;
+            if (bin >= 0 && bin < 30 && bin != ind1 && bin != ind2 && bin != ind3) {
+                mF[i] = -1;                                       /* vpMapPointMatches[...] = NULL; nmatches-- */
+                if (ko) ko[ra].accepted = 2;
+            }
+        }
+        __syncthreads();
+    }
+    int cnt = 0;
+    for (int i = tid; i < rowStride; i += SB_NT) cnt += mF[i] >= 0 ? 1 : 0;
+#pragma unroll
+    for (int o = 16; o; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+    __shared__ int s_total;
+    if (tid == 0) s_total = 0;
+    __syncthreads();
+    if ((tid & 31) == 0) atomicAdd(&s_total, cnt);
+    __syncthreads();
+    if (tid == 0 && nmatches) nmatches[pr] = s_total;
+}
+
 static int bow_norm_of(int scoring) { return scoring == 5 ? 0 : (scoring == 1 ? 2 : 1); }   /* ScoringObject.h:73-90 */
 
 extern "C" {
@@ -331,6 +487,87 @@ int orbfe_bow_device_views(orbfe_vocabulary* v, const int32_t** d_feat_word, con
     if (d_fv_starts) *d_fv_starts = v->fvStarts;
     if (d_fv_feats) *d_fv_feats = v->fvFeats;
     if (d_fv_count) *d_fv_count = v->fvCount;
+    return ORBFE_OK;
+}
+
+int orbfe_search_by_bow_device(int device, int npairs, int max_features, const int32_t* d_pair_kf, const int32_t* d_pair_f, const uint8_t* d_desc,
+                               const orbfe_keypoint* d_kps, int row_stride, const int32_t* d_fv_nodes, const int32_t* d_fv_starts, const int32_t* d_fv_feats,
+                               const int32_t* d_fv_count, const uint8_t* d_has_map_point, int th_low, float nnratio, int check_orientation,
+                               int32_t* d_match_f, orbfe_match* d_kf_out, int32_t* d_nmatches, void* stream) {
+    if (npairs < 1 || !d_pair_kf || !d_pair_f || !d_desc || !d_fv_nodes || !d_fv_starts || !d_fv_feats || !d_fv_count || !d_match_f || row_stride < 1 ||
+        (check_orientation && !d_kps)) { orbfe_set_error("bad argument"); return ORBFE_E_INVALID; }
+    if (max_features < 1 || max_features > BOW_MAXF || row_stride > BOW_MAXF) { orbfe_set_error("at most %d features per frame", BOW_MAXF); return ORBFE_E_CAPACITY; }
+    if ((uintptr_t)d_desc & 15) { orbfe_set_error("descriptor array must be 16-byte aligned"); return ORBFE_E_INVALID; }
+    ORBFE_CUDA(cudaSetDevice(device));
+    k_search_by_bow<<<npairs, SB_NT, 0, (cudaStream_t)stream>>>(max_features, d_pair_kf, d_pair_f, (const uint4*)d_desc, d_kps, row_stride, d_fv_nodes, d_fv_starts,
+                                                                d_fv_feats, d_fv_count, d_has_map_point, th_low, nnratio, check_orientation ? 1 : 0, d_match_f,
+                                                                d_kf_out, d_nmatches);
+    ORBFE_CUDA(cudaGetLastError());
+    return ORBFE_OK;
+}
+
+/* one (keyframe, frame) pair over host memory: the feature vectors are the fv_* arrays orbfe_bow_result returns */
+int orbfe_search_by_bow(int device, const uint8_t* desc_kf, const orbfe_keypoint* kps_kf, int n_kf, const int32_t* fv_nodes_kf, const int32_t* fv_starts_kf,
+                        const int32_t* fv_feats_kf, int nfv_kf, const uint8_t* has_map_point, const uint8_t* desc_f, const orbfe_keypoint* kps_f, int n_f,
+                        const int32_t* fv_nodes_f, const int32_t* fv_starts_f, const int32_t* fv_feats_f, int nfv_f, int th_low, float nnratio,
+                        int check_orientation, int32_t* match_f, orbfe_match* kf_out, int* nmatches) {
+    if (n_kf < 0 || n_f < 0 || nfv_kf < 0 || nfv_f < 0 || !match_f || (n_kf && !desc_kf) || (n_f && !desc_f) || (check_orientation && (!kps_kf || !kps_f)) ||
+        (nfv_kf && (!fv_nodes_kf || !fv_starts_kf || !fv_feats_kf)) || (nfv_f && (!fv_nodes_f || !fv_starts_f || !fv_feats_f))) { orbfe_set_error("bad argument"); return ORBFE_E_INVALID; }
+    const int S = std::max(std::max(n_kf, n_f), 1);
+    if (S > BOW_MAXF) { orbfe_set_error("at most %d features per frame", BOW_MAXF); return ORBFE_E_CAPACITY; }
+    if (nmatches) *nmatches = 0;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev) {
+        orbfe_set_error("no usable CUDA device %d (found %d); this library has no CPU path", device, ndev);
+        return ORBFE_E_CUDA;
+    }
+    ORBFE_CUDA(cudaSetDevice(device));
+    /* two frames (0 = keyframe, 1 = frame) in the strided layout of the batch entry point */
+    std::vector<uint8_t> hDesc((size_t)2 * S * 32, 0), hMp((size_t)2 * S, 1);
+    std::vector<orbfe_keypoint> hKps((size_t)2 * S);
+    std::vector<int32_t> hNodes((size_t)2 * S, 0), hStarts((size_t)2 * (S + 1), 0), hFeats((size_t)2 * S, 0), hCount(2), hPair(2);
+    memset(hKps.data(), 0, hKps.size() * sizeof(orbfe_keypoint));
+    if (n_kf) memcpy(hDesc.data(), desc_kf, (size_t)n_kf * 32);
+    if (n_f) memcpy(hDesc.data() + (size_t)S * 32, desc_f, (size_t)n_f * 32);
+    if (kps_kf && n_kf) memcpy(hKps.data(), kps_kf, (size_t)n_kf * sizeof(orbfe_keypoint));
+    if (kps_f && n_f) memcpy(hKps.data() + S, kps_f, (size_t)n_f * sizeof(orbfe_keypoint));
+    if (has_map_point && n_kf) memcpy(hMp.data(), has_map_point, (size_t)n_kf);
+    if (nfv_kf > S || nfv_f > S) { orbfe_set_error("feature vector longer than the frame"); return ORBFE_E_INVALID; }
+    if (nfv_kf) {
+        if (fv_starts_kf[nfv_kf] > S) { orbfe_set_error("feature vector longer than the frame"); return ORBFE_E_INVALID; }
+        memcpy(hNodes.data(), fv_nodes_kf, (size_t)nfv_kf * 4); memcpy(hStarts.data(), fv_starts_kf, (size_t)(nfv_kf + 1) * 4);
+        memcpy(hFeats.data(), fv_feats_kf, (size_t)fv_starts_kf[nfv_kf] * 4);
+    }
+    if (nfv_f) {
+        if (fv_starts_f[nfv_f] > S) { orbfe_set_error("feature vector longer than the frame"); return ORBFE_E_INVALID; }
+        memcpy(hNodes.data() + S, fv_nodes_f, (size_t)nfv_f * 4); memcpy(hStarts.data() + S + 1, fv_starts_f, (size_t)(nfv_f + 1) * 4);
+        memcpy(hFeats.data() + S, fv_feats_f, (size_t)fv_starts_f[nfv_f] * 4);
+    }
+    hCount[0] = nfv_kf; hCount[1] = nfv_f; hPair[0] = 0; hPair[1] = 1;
+    size_t off = 0;
+    auto take = [&](size_t bytes) { const size_t o = off; off += (bytes + 255) & ~(size_t)255; return o; };
+    const size_t oDesc = take(hDesc.size()), oKps = take(hKps.size() * sizeof(orbfe_keypoint)), oMp = take(hMp.size()), oNodes = take(hNodes.size() * 4);
+    const size_t oStarts = take(hStarts.size() * 4), oFeats = take(hFeats.size() * 4), oCount = take(8), oPair = take(8), oMatch = take((size_t)S * 4);
+    const size_t oKf = take((size_t)S * sizeof(orbfe_match)), oNm = take(4);
+    uint8_t* d = nullptr;
+    ORBFE_CUDA(cudaMalloc((void**)&d, off));
+    cudaError_t e = cudaMemcpy(d + oDesc, hDesc.data(), hDesc.size(), cudaMemcpyHostToDevice);
+#define SB_UP(o, v, bytes) if (e == cudaSuccess) e = cudaMemcpy(d + (o), (v), (bytes), cudaMemcpyHostToDevice)
+    SB_UP(oKps, hKps.data(), hKps.size() * sizeof(orbfe_keypoint)); SB_UP(oMp, hMp.data(), hMp.size()); SB_UP(oNodes, hNodes.data(), hNodes.size() * 4);
+    SB_UP(oStarts, hStarts.data(), hStarts.size() * 4); SB_UP(oFeats, hFeats.data(), hFeats.size() * 4); SB_UP(oCount, hCount.data(), 8); SB_UP(oPair, hPair.data(), 8);
+#undef SB_UP
+    int rc = ORBFE_OK;
+    if (e == cudaSuccess)
+        rc = orbfe_search_by_bow_device(device, 1, S, (const int32_t*)(d + oPair), (const int32_t*)(d + oPair) + 1, d + oDesc, (const orbfe_keypoint*)(d + oKps), S,
+                                        (const int32_t*)(d + oNodes), (const int32_t*)(d + oStarts), (const int32_t*)(d + oFeats), (const int32_t*)(d + oCount),
+                                        d + oMp, th_low, nnratio, check_orientation, (int32_t*)(d + oMatch), (orbfe_match*)(d + oKf), (int32_t*)(d + oNm), nullptr);
+    if (rc == ORBFE_OK && e == cudaSuccess) e = cudaDeviceSynchronize();
+    if (rc == ORBFE_OK && e == cudaSuccess && n_f) e = cudaMemcpy(match_f, d + oMatch, (size_t)n_f * 4, cudaMemcpyDeviceToHost);
+    if (rc == ORBFE_OK && e == cudaSuccess && kf_out && n_kf) e = cudaMemcpy(kf_out, d + oKf, (size_t)n_kf * sizeof(orbfe_match), cudaMemcpyDeviceToHost);
+    if (rc == ORBFE_OK && e == cudaSuccess && nmatches) e = cudaMemcpy(nmatches, d + oNm, 4, cudaMemcpyDeviceToHost);
+    cudaFree(d);
+    if (rc != ORBFE_OK) return rc;
+    if (e != cudaSuccess) return orbfe_cuda_fail(e, "search_by_bow");
     return ORBFE_OK;
 }
 

@@ -174,3 +174,143 @@ def test_gpu_transform_chained_after_extraction():
         assert same(voc.result(f, int(cnt[f])), orc.transform(desc[f, :cnt[f]], 2)), "frame %d" % f
     assert cnt[2] == 0 and len(voc.result(2, 0)["bow_words"]) == 0
     voc.close(); ex.close()
+
+
+# ------------------------------------------------------------------------------------------------------ SearchByBoW
+def make_pair(seed, rows, n_kf, n_f, turn=25.0):
+    """A keyframe and a frame looking at the same scene: most frame descriptors are keyframe descriptors with a few bits flipped."""
+    from oracle.orb_oracle import KP_DTYPE
+    rng = np.random.RandomState(seed)
+    d_kf = make_features(seed, rows[2], n_kf)
+    src = rng.randint(0, max(n_kf, 1), n_f)
+    d_f = d_kf[src].copy() if n_kf else np.zeros((n_f, 32), np.uint8)
+    for i in range(n_f):
+        nb = int(rng.randint(0, 24)) if rng.uniform() < 0.8 else 120
+        for b in rng.choice(256, size=nb, replace=False):
+            d_f[i, b >> 3] ^= np.uint8(1 << (b & 7))
+    k_kf, k_f = np.zeros(n_kf, KP_DTYPE), np.zeros(n_f, KP_DTYPE)
+    k_kf["angle"] = rng.uniform(0, 360, n_kf)
+    k_f["angle"] = (k_kf["angle"][src] - turn + np.where(rng.uniform(size=n_f) < 0.85, rng.uniform(-5, 5, n_f), rng.uniform(0, 360, n_f))) % 360 if n_kf else 0
+    has_mp = (rng.uniform(size=n_kf) < 0.8).astype(np.uint8)
+    return d_kf, k_kf, has_mp, d_f, k_f
+
+
+def python_search_by_bow(d_kf, k_kf, fv_kf, has_mp, d_f, k_f, fv_f, th_low, ratio, check_ori):
+    """ORBmatcher::SearchByBoW(pKF, F, ...) (F.Nleft == -1) in plain Python, written from src/ORBmatcher.cc:269-470."""
+    f32 = np.float32
+    match = np.full(len(d_f), -1, np.int32)
+    hist = [[] for _ in range(30)]
+    nm = 0
+    for node in sorted(set(fv_kf) & set(fv_f)):          # the lockstep walk visits exactly the common nodes, in key order
+        for ikf in fv_kf[node]:
+            if not has_mp[ikf]:
+                continue
+            b1, b2, bi = 256, 256, -1
+            for i_f in fv_f[node]:
+                if match[i_f] >= 0:
+                    continue
+                d = int(POPC[d_kf[ikf] ^ d_f[i_f]].sum())
+                if d < b1:
+                    b2, b1, bi = b1, d, i_f
+                elif d < b2:
+                    b2 = d
+            if b1 <= th_low and f32(b1) < f32(ratio) * f32(b2):
+                match[bi] = ikf
+                nm += 1
+                if check_ori:
+                    rot = f32(k_kf["angle"][ikf]) - f32(k_f["angle"][bi])
+                    if rot < 0:
+                        rot = f32(rot + f32(360))
+                    b = int(np.floor(abs(float(f32(rot * f32(f32(1) / f32(30))))) + 0.5))
+                    hist[0 if b == 30 else b].append(bi)
+    if check_ori:
+        ind, mx = [-1, -1, -1], [0, 0, 0]
+        for i, h in enumerate(hist):
+            sz = len(h)
+            if sz > mx[0]:
+                mx = [sz, mx[0], mx[1]]; ind = [i, ind[0], ind[1]]
+            elif sz > mx[1]:
+                mx = [mx[0], sz, mx[1]]; ind = [ind[0], i, ind[1]]
+            elif sz > mx[2]:
+                mx[2] = sz; ind[2] = i
+        if f32(mx[1]) < f32(0.1) * f32(mx[0]):
+            ind[1] = ind[2] = -1
+        elif f32(mx[2]) < f32(0.1) * f32(mx[0]):
+            ind[2] = -1
+        for i in range(30):
+            if i not in ind:
+                for bi in hist[i]:
+                    match[bi] = -1
+                    nm -= 1
+    return match, nm
+
+
+SB_CONFIGS = [(4, 3, 1, 21, 400, 450), (10, 3, 2, 22, 800, 700), (3, 4, 3, 23, 600, 600), (10, 4, 2, 24, 1200, 1300)]   # k, L, levelsup, seed, nKF, nF
+
+
+def test_oracle_search_by_bow_matches_python():
+    for k, L, levelsup, seed, n_kf, n_f in SB_CONFIGS:
+        rows = make_vocabulary(seed, k, L)
+        voc = O.OracleVocabulary(k, L, 0, 0, *rows)
+        d_kf, k_kf, has_mp, d_f, k_f = make_pair(seed, rows, n_kf, n_f)
+        fv_kf, fv_f = voc.transform(d_kf, levelsup)["feat_vec"], voc.transform(d_f, levelsup)["feat_vec"]
+        for ori in (True, False):
+            match, kf_out, nm = O.search_by_bow(d_kf, k_kf, fv_kf, has_mp, d_f, k_f, fv_f, 50, 0.7, ori)
+            want, wnm = python_search_by_bow(d_kf, k_kf, fv_kf, has_mp, d_f, k_f, fv_f, 50, 0.7, ori)
+            assert np.array_equal(match, want) and nm == wnm, (k, L, levelsup, ori)
+            assert nm > 50 and (not ori or (kf_out["accepted"] == 2).sum() > 0)
+
+
+@pytest.mark.gpu
+def test_gpu_search_by_bow_matches_oracle():
+    from orb_slam3_detailed_comments_kor_b200 import bow as B
+    for k, L, levelsup, seed, n_kf, n_f in SB_CONFIGS + [(2, 2, 1, 25, 900, 1000), (10, 4, 2, 26, 4096, 4096), (10, 3, 1, 27, 0, 50), (10, 3, 1, 28, 40, 0)]:
+        rows = make_vocabulary(seed, k, L)
+        voc = O.OracleVocabulary(k, L, 0, 0, *rows)
+        d_kf, k_kf, has_mp, d_f, k_f = make_pair(seed, rows, n_kf, n_f)
+        fv_kf, fv_f = voc.transform(d_kf, levelsup)["feat_vec"], voc.transform(d_f, levelsup)["feat_vec"]
+        for ori in (True, False):
+            want = O.search_by_bow(d_kf, k_kf, fv_kf, has_mp, d_f, k_f, fv_f, 50, 0.7, ori)
+            got = B.search_by_bow(d_kf, k_kf, fv_kf, has_mp, d_f, k_f, fv_f, 50, 0.7, ori)
+            assert np.array_equal(got[0], want[0]) and got[2] == want[2], (k, L, levelsup, n_kf, n_f, ori)
+            assert np.array_equal(got[1], want[1]), (k, L, levelsup, n_kf, n_f, ori)
+
+
+@pytest.mark.gpu
+def test_gpu_extract_bow_search_chain_on_device():
+    """Tracking's relocalisation path end to end on the device: extract a batch, ComputeBoW, SearchByBoW between frame pairs."""
+    import ctypes as C
+    import torch
+    from orb_slam3_detailed_comments_kor_b200 import ORBextractor, synth, _lib
+    from orb_slam3_detailed_comments_kor_b200.bow import ORBVocabulary
+    W, H, params, nb = 752, 480, (1200, 1.2, 8, 20, 7), 6
+    imgs = np.stack([synth.stereo_pair(80 + i // 2, W, H)[i % 2] for i in range(nb)])     # (L, R) of three scenes: 0-1, 2-3, 4-5 overlap
+    ex = ORBextractor(*params, width=W, height=H, max_batch=nb)
+    cnt, mono, kps, desc = ex.extract_batch_host(imgs, (0, 0))
+    rows = make_vocabulary(33, 10, 4)
+    voc = ORBVocabulary(10, 4, 0, 0, *rows, max_features=ex.capacity, max_batch=nb)
+    orc = O.OracleVocabulary(10, 4, 0, 0, *rows)
+    views = [C.c_void_p() for _ in range(4)]
+    _lib.check(_lib.lib().orbfe_batch_device_views(ex.handle, *[C.byref(v) for v in views]))
+    d_kps, d_desc, d_cnt = views[0].value, views[1].value, views[2].value
+    st = torch.cuda.Stream()
+    voc.transform_batch_device(d_desc, ex.capacity, d_cnt, nb, 2, stream=st.cuda_stream)
+    bv = [C.c_void_p() for _ in range(9)]
+    _lib.check(_lib.lib().orbfe_bow_device_views(voc.handle, *[C.byref(v) for v in bv]))
+    pairs_kf, pairs_f = np.array([0, 2, 4, 1, 0], np.int32), np.array([1, 3, 5, 0, 4], np.int32)
+    with torch.cuda.stream(st):
+        d_pk, d_pf = torch.from_numpy(pairs_kf).cuda(), torch.from_numpy(pairs_f).cuda()
+        d_match = torch.zeros((len(pairs_kf), ex.capacity), dtype=torch.int32, device="cuda")
+        d_nm = torch.zeros(len(pairs_kf), dtype=torch.int32, device="cuda")
+        _lib.check(_lib.lib().orbfe_search_by_bow_device(0, len(pairs_kf), ex.capacity, d_pk.data_ptr(), d_pf.data_ptr(), d_desc, d_kps, ex.capacity,
+                                                         bv[5].value, bv[6].value, bv[7].value, bv[8].value, None, 50, C.c_float(0.7), 1,
+                                                         d_match.data_ptr(), None, d_nm.data_ptr(), st.cuda_stream))
+        match, nm = d_match.cpu().numpy(), d_nm.cpu().numpy()
+    st.synchronize()
+    for p, (a, b) in enumerate(zip(pairs_kf, pairs_f)):
+        fa, fb = orc.transform(desc[a, :cnt[a]], 2)["feat_vec"], orc.transform(desc[b, :cnt[b]], 2)["feat_vec"]
+        want, _, wnm = O.search_by_bow(desc[a, :cnt[a]], kps[a, :cnt[a]], fa, None, desc[b, :cnt[b]], kps[b, :cnt[b]], fb, 50, 0.7, True)
+        assert np.array_equal(match[p, :cnt[b]], want) and nm[p] == wnm, "pair %d" % p
+        assert (match[p, cnt[b]:] == -1).all()
+    assert nm[:3].sum() > 0                              # (a random vocabulary separates real descriptors poorly: few, but some, matches)
+    voc.close(); ex.close()
