@@ -95,6 +95,14 @@ int orbfe_extract_batch_device(orbfe_extractor* ex, const uint8_t* d_images, int
  * kps: nframes*cap entries, desc: nframes*cap*32 bytes, n / mono_index: nframes ints.  Synchronous. */
 int orbfe_extract_batch_host(orbfe_extractor* ex, const uint8_t* h_images, int nframes, int lap0, int lap1,
                              orbfe_keypoint* kps, uint8_t* desc, int cap, int32_t* n, int32_t* mono_index);
+/* Frame's stereo constructor for a batch of pairs in one call (src/Frame.cc:104-178: the two ExtractORB threads, then
+ * ComputeStereoMatches): uploads, both extractions, the stereo matching and the downloads are pipelined over chunks of frames on
+ * the two objects' streams, from one host thread.  Outputs as orbfe_extract_batch_host for each side (cap >= the keypoint
+ * capacity; any output pointer may be NULL), plus mvuRight / mvDepth of every pair in u_right / depth [nframes*cap] (-1 = no match;
+ * entries beyond a frame's keypoint count are unspecified).  mbf, min_d, max_d as orbfe_stereo_match_batch_device.  Synchronous. */
+int orbfe_stereo_frames_batch_host(orbfe_extractor* exL, orbfe_extractor* exR, const uint8_t* h_left, const uint8_t* h_right, int nframes, int lap0,
+                                   int lap1, float mbf, float min_d, float max_d, orbfe_keypoint* kps_l, uint8_t* desc_l, int32_t* n_l, int32_t* mono_l,
+                                   orbfe_keypoint* kps_r, uint8_t* desc_r, int32_t* n_r, int32_t* mono_r, int cap, float* u_right, float* depth);
 /* Fetch what the last batch call left on the device (synchronises the object's stream). */
 int orbfe_batch_counts(orbfe_extractor* ex, int nframes, int32_t* n, int32_t* mono_index);
 int orbfe_batch_result(orbfe_extractor* ex, int frame, orbfe_keypoint* kps, uint8_t* desc, int cap, int* n,

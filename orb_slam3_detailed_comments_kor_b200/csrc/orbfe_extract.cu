@@ -1286,7 +1286,7 @@ int orbfe_configure_kernels(int quadSmem, int fastSmem) {
 }
 
 /* The per-frame buffers as seen by a launch whose frame 0 is the object's frame f0 (chunked host pipeline). */
-static ExBuffers shift_frames(const ExBuffers& b, const ExDesc& d, int f0) {
+ExBuffers orbfe_shift_frames(const ExBuffers& b, const ExDesc& d, int f0) {
     ExBuffers s = b;
     const size_t f = (size_t)f0;
     s.pyr += f * d.pyrSlab; s.blur += f * d.blurSlab;
@@ -1303,7 +1303,7 @@ static ExBuffers shift_frames(const ExBuffers& b, const ExDesc& d, int f0) {
  * frame0 .. frame0+nframes-1 (frame0 != 0 only in the chunked host pipeline, which runs its chunks in stream order). */
 int orbfe_launch_extract(orbfe_extractor* ex, const uint8_t* d_images, int nframes, int lap0, int lap1, cudaStream_t st, int frame0) {
     const ExDesc& d = ex->d;
-    const ExBuffers xb = frame0 ? shift_frames(ex->b, d, frame0) : ex->b;
+    const ExBuffers xb = frame0 ? orbfe_shift_frames(ex->b, d, frame0) : ex->b;
     const bool prof = ex->profiling != 0 && frame0 == 0;
     int e = 0;
 #define STAGE_MARK() do { if (prof) ORBFE_CUDA(cudaEventRecord(ex->ev[e++], st)); } while (0)

@@ -520,6 +520,68 @@ int orbfe_extract_batch_host(orbfe_extractor* ex, const uint8_t* h_images, int n
     return ORBFE_OK;
 }
 
+int orbfe_stereo_frames_batch_host(orbfe_extractor* exL, orbfe_extractor* exR, const uint8_t* h_left, const uint8_t* h_right, int nframes, int lap0,
+                                   int lap1, float mbf, float min_d, float max_d, orbfe_keypoint* kps_l, uint8_t* desc_l, int32_t* n_l, int32_t* mono_l,
+                                   orbfe_keypoint* kps_r, uint8_t* desc_r, int32_t* n_r, int32_t* mono_r, int cap, float* u_right, float* depth) {
+    if (!exL || !exR || !h_left || !h_right) { orbfe_set_error("null argument"); return ORBFE_E_INVALID; }
+    if (exL == exR || exL->device != exR->device || exL->d.W != exR->d.W || exL->d.H != exR->d.H || exL->d.kpCap != exR->d.kpCap ||
+        exL->d.nlevels != exR->d.nlevels || exL->hostChunk != exR->hostChunk) { orbfe_set_error("left/right extractors must be two objects of the same geometry on one device"); return ORBFE_E_INVALID; }
+    if (nframes < 1 || nframes > exL->maxBatch || nframes > exR->maxBatch) { orbfe_set_error("nframes %d outside [1, max_batch]", nframes); return ORBFE_E_CAPACITY; }
+    const int kc = exL->d.kpCap;
+    if (cap < kc) { orbfe_set_error("cap %d < keypoint capacity %d", cap, kc); return ORBFE_E_CAPACITY; }
+    ORBFE_CUDA(cudaSetDevice(exL->device));
+    const size_t frameBytes = (size_t)exL->d.W * exL->d.H;
+    exL->lastBatch = exR->lastBatch = nframes;
+    cudaStream_t sl = exL->stream, sr = exR->stream, in = exL->copyIn, out = exL->copyOut;
+    /* per chunk: upload L then R on one copy stream (so the left extraction can start after half the upload), extract L and R on
+     * their own streams, match on the left stream once the right one is done, download everything on the other copy stream */
+    const int C = exL->hostChunk;
+    for (int k = 0, f0 = 0; f0 < nframes; k++, f0 += C) {
+        const int nf = std::min(C, nframes - f0);
+        ORBFE_CUDA(cudaMemcpyAsync(exL->inputStage + (size_t)f0 * frameBytes, h_left + (size_t)f0 * frameBytes, frameBytes * nf, cudaMemcpyHostToDevice, in));
+        ORBFE_CUDA(cudaEventRecord(exL->evIn[k], in));
+        ORBFE_CUDA(cudaMemcpyAsync(exR->inputStage + (size_t)f0 * frameBytes, h_right + (size_t)f0 * frameBytes, frameBytes * nf, cudaMemcpyHostToDevice, in));
+        ORBFE_CUDA(cudaEventRecord(exR->evIn[k], in));
+        ORBFE_CUDA(cudaStreamWaitEvent(sl, exL->evIn[k], 0));
+        int rc = orbfe_launch_extract(exL, exL->inputStage + (size_t)f0 * frameBytes, nf, lap0, lap1, sl, f0);
+        if (rc) return rc;
+        ORBFE_CUDA(cudaStreamWaitEvent(sr, exR->evIn[k], 0));
+        rc = orbfe_launch_extract(exR, exR->inputStage + (size_t)f0 * frameBytes, nf, lap0, lap1, sr, f0);
+        if (rc) return rc;
+        ORBFE_CUDA(cudaEventRecord(exR->evDone[k], sr));
+        ORBFE_CUDA(cudaStreamWaitEvent(sl, exR->evDone[k], 0));
+        rc = orbfe_launch_stereo(exL, exR, nf, f0, mbf, min_d, max_d, sl);
+        if (rc) return rc;
+        ORBFE_CUDA(cudaEventRecord(exL->evDone[k], sl));
+        ORBFE_CUDA(cudaStreamWaitEvent(out, exL->evDone[k], 0));
+        orbfe_extractor* exs[2] = {exL, exR};
+        orbfe_keypoint* kk[2] = {kps_l, kps_r};
+        uint8_t* dd[2] = {desc_l, desc_r};
+        for (int s = 0; s < 2; s++) {
+            orbfe_extractor* ex = exs[s];
+            ORBFE_CUDA(cudaMemcpyAsync(ex->hCount + f0, ex->b.count + f0, nf * sizeof(int), cudaMemcpyDeviceToHost, out));
+            ORBFE_CUDA(cudaMemcpyAsync(ex->hMono + f0, ex->b.mono + f0, nf * sizeof(int), cudaMemcpyDeviceToHost, out));
+            if (kk[s]) ORBFE_CUDA(cudaMemcpy2DAsync(kk[s] + (size_t)f0 * cap, (size_t)cap * sizeof(orbfe_keypoint), ex->b.kps + (size_t)f0 * kc, (size_t)kc * sizeof(orbfe_keypoint),
+                                                   (size_t)kc * sizeof(orbfe_keypoint), nf, cudaMemcpyDeviceToHost, out));
+            if (dd[s]) ORBFE_CUDA(cudaMemcpy2DAsync(dd[s] + (size_t)f0 * cap * 32, (size_t)cap * 32, ex->b.desc + (size_t)f0 * kc * 32, (size_t)kc * 32, (size_t)kc * 32, nf,
+                                                   cudaMemcpyDeviceToHost, out));
+        }
+        const size_t w = (size_t)kc * sizeof(float);
+        if (u_right) ORBFE_CUDA(cudaMemcpy2DAsync(u_right + (size_t)f0 * cap, (size_t)cap * sizeof(float), exL->b.uRight + (size_t)f0 * kc, w, w, nf, cudaMemcpyDeviceToHost, out));
+        if (depth) ORBFE_CUDA(cudaMemcpy2DAsync(depth + (size_t)f0 * cap, (size_t)cap * sizeof(float), exL->b.depth + (size_t)f0 * kc, w, w, nf, cudaMemcpyDeviceToHost, out));
+    }
+    ORBFE_CUDA(cudaStreamSynchronize(out));
+    ORBFE_CUDA(cudaStreamSynchronize(sl));
+    ORBFE_CUDA(cudaStreamSynchronize(sr));
+    for (int f = 0; f < nframes; f++) {
+        if (n_l) n_l[f] = exL->hCount[f];
+        if (mono_l) mono_l[f] = exL->hMono[f];
+        if (n_r) n_r[f] = exR->hCount[f];
+        if (mono_r) mono_r[f] = exR->hMono[f];
+    }
+    return ORBFE_OK;
+}
+
 int orbfe_extract(orbfe_extractor* ex, const uint8_t* image, int rows, int cols, size_t step, int lap0, int lap1,
                   orbfe_keypoint* kps, uint8_t* desc, int cap, int* n, int* mono_index) {
     if (n) *n = 0;

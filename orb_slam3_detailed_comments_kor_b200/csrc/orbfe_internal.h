@@ -142,6 +142,11 @@ struct orbfe_extractor {
     int* hMono;
 };
 
+/* views of the per-frame buffers that start at frame f0 (kernels index frames from blockIdx) */
+ExBuffers orbfe_shift_frames(const ExBuffers& b, const ExDesc& d, int f0);
+/* Frame::ComputeStereoMatches kernels for frames [frame0, frame0 + nframes) of two extractors, enqueued on st */
+int orbfe_launch_stereo(orbfe_extractor* exL, orbfe_extractor* exR, int nframes, int frame0, float mbf, float minD, float maxD, cudaStream_t st);
+
 void orbfe_set_error(const char* fmt, ...);
 int orbfe_cuda_fail(cudaError_t e, const char* what);
 #define ORBFE_CUDA(call)                                          \

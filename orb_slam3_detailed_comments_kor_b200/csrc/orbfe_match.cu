@@ -419,6 +419,17 @@ __global__ void __launch_bounds__(DD_WARPS * 32) k_distinctive(const uint4* __re
     if (lane == 0) { bestIdx[p] = (int)(best & 0xFFFFu); if (bestMedian) bestMedian[p] = (int)(best >> 16); }
 }
 
+int orbfe_launch_stereo(orbfe_extractor* exL, orbfe_extractor* exR, int nframes, int frame0, float mbf, float minD, float maxD, cudaStream_t st) {
+    const ExBuffers bl = frame0 ? orbfe_shift_frames(exL->b, exL->d, frame0) : exL->b;
+    const ExBuffers br = frame0 ? orbfe_shift_frames(exR->b, exR->d, frame0) : exR->b;
+    k_stereo_bucket<<<nframes, 256, (exR->d.stBands + 1) * sizeof(int), st>>>(exR->d, br);
+    k_stereo_match<<<dim3((exL->d.kpCap + ST_KPB - 1) / ST_KPB, nframes), ST_NT, 0, st>>>(exL->d, bl, br, mbf, minD, maxD);
+    k_stereo_median<<<nframes, 256, 0, st>>>(exL->d, bl);
+    exL->launches += 3;
+    ORBFE_CUDA(cudaGetLastError());
+    return ORBFE_OK;
+}
+
 extern "C" {
 
 int orbfe_stereo_match_batch_device(orbfe_extractor* exL, orbfe_extractor* exR, int nframes, float mbf, float minD, float maxD, void* stream) {
@@ -432,11 +443,7 @@ int orbfe_stereo_match_batch_device(orbfe_extractor* exL, orbfe_extractor* exR, 
     if (prof && exL->stereoPending) { int rc = orbfe_collect_stage_times(exL); if (rc) return rc; }
     cudaEvent_t* ev = exL->ev + ORBFE_NUM_STAGES + 1; /* two private events: the extractor's own stay untouched */
     if (prof) ORBFE_CUDA(cudaEventRecord(ev[0], st));
-    k_stereo_bucket<<<nframes, 256, (exR->d.stBands + 1) * sizeof(int), st>>>(exR->d, exR->b);
-    k_stereo_match<<<dim3((exL->d.kpCap + ST_KPB - 1) / ST_KPB, nframes), ST_NT, 0, st>>>(exL->d, exL->b, exR->b, mbf, minD, maxD);
-    k_stereo_median<<<nframes, 256, 0, st>>>(exL->d, exL->b);
-    exL->launches += 3;
-    ORBFE_CUDA(cudaGetLastError());
+    { int rc = orbfe_launch_stereo(exL, exR, nframes, 0, mbf, minD, maxD, st); if (rc) return rc; }
     if (prof) {
         /* stereo is short: time both kernels as one span, reported under "stereo match" */
         ORBFE_CUDA(cudaEventRecord(ev[1], st));

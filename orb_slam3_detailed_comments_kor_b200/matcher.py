@@ -90,6 +90,23 @@ def compute_stereo_matches(exL, exR, nframes, mbf, minD, maxD, stream=None):
                                                      C.c_void_p(stream) if stream else None))
 
 
+def stereo_frames_batch_host(exL, exR, left, right, mbf, minD, maxD, vLappingArea=(0, 0), out=None):
+    """Frame's stereo constructor for a batch of pairs (src/Frame.cc:104-178): both extractions and ComputeStereoMatches,
+    pipelined over chunks inside one call.  left / right: [n, H, W] u8 host arrays.  Returns
+    (cntL, monoL, kpsL, descL, cntR, monoR, kpsR, descR, uRight[n, cap], depth[n, cap])."""
+    from ._lib import KP_DTYPE
+    L = np.ascontiguousarray(left, np.uint8); R = np.ascontiguousarray(right, np.uint8)
+    nf, cap = L.shape[0], exL.capacity
+    if out is None:
+        side = lambda: (np.zeros(nf, np.int32), np.zeros(nf, np.int32), np.zeros((nf, cap), KP_DTYPE), np.zeros((nf, cap, 32), np.uint8))  # noqa: E731
+        out = side() + side() + (np.zeros((nf, cap), np.float32), np.zeros((nf, cap), np.float32))
+    cl, ml, kl, dl, cr, mr, kr, dr, u, d = out
+    check(_lib.lib().orbfe_stereo_frames_batch_host(exL.handle, exR.handle, ptr(L), ptr(R), nf, int(vLappingArea[0]), int(vLappingArea[1]),
+                                                    C.c_float(mbf), C.c_float(minD), C.c_float(maxD), ptr(kl), ptr(dl), ptr(cl), ptr(ml),
+                                                    ptr(kr), ptr(dr), ptr(cr), ptr(mr), cap, ptr(u), ptr(d)))
+    return out
+
+
 def stereo_result(exL, frame):
     u = np.zeros(exL.capacity, np.float32)
     d = np.zeros(exL.capacity, np.float32)

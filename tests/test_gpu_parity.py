@@ -244,6 +244,35 @@ def test_stereo_batch_and_no_match_frame():
     exL.close(); exR.close()
 
 
+def test_stereo_frames_pipeline_matches_separate_calls():
+    """orbfe_stereo_frames_batch_host (upload, both extractions, stereo matching, download pipelined over chunks in one call) must
+    return exactly what extract_batch_host x 2 + compute_stereo_matches return; 150 pairs = three chunks, one of them short."""
+    W, H, params, nb = 320, 240, (500, 1.2, 8, 20, 7), 150
+    pairs = [synth.stereo_pair(400 + i, W, H) for i in range(nb)]
+    Ls = np.stack([p[0] for p in pairs]); Rs = np.stack([p[1] for p in pairs])
+    exL = ORBextractor(*params, width=W, height=H, max_batch=nb)
+    exR = ORBextractor(*params, width=W, height=H, max_batch=nb)
+    cl, ml, kl, dl, cr, mr, kr, dr, u, d = [a.copy() for a in M.stereo_frames_batch_host(exL, exR, Ls, Rs, 40.0, 0.0, 300.0, (0, 0))]
+    wl = [a.copy() for a in exL.extract_batch_host(Ls, (0, 0))]
+    wr = [a.copy() for a in exR.extract_batch_host(Rs, (0, 0))]
+    M.compute_stereo_matches(exL, exR, nb, 40.0, 0.0, 300.0)
+    assert np.array_equal(cl, wl[0]) and np.array_equal(ml, wl[1]) and np.array_equal(cr, wr[0]) and np.array_equal(mr, wr[1])
+    matched = 0
+    for f in range(nb):
+        assert np.array_equal(kl[f, :cl[f]], wl[2][f, :cl[f]]) and np.array_equal(dl[f, :cl[f]], wl[3][f, :cl[f]]), "left frame %d" % f
+        assert np.array_equal(kr[f, :cr[f]], wr[2][f, :cr[f]]) and np.array_equal(dr[f, :cr[f]], wr[3][f, :cr[f]]), "right frame %d" % f
+        wu, wd = M.stereo_result(exL, f)
+        assert np.array_equal(u[f, :cl[f]], wu) and np.array_equal(d[f, :cl[f]], wd), "stereo of pair %d" % f
+        matched += int((wu >= 0).sum())
+    assert matched > 20 * nb
+    # and against the oracle on one pair of the last (short) chunk
+    oL, oR = O.OracleExtractor(*params), O.OracleExtractor(*params)
+    _, okL, odL = oL(Ls[149]); _, okR, odR = oR(Rs[149])
+    kept, ou, od = O.stereo_match(oL, oR, okL, odL, okR, odR, 40.0, 0.0, 300.0)
+    assert np.array_equal(u[149, :cl[149]], ou) and np.array_equal(d[149, :cl[149]], od)
+    exL.close(); exR.close()
+
+
 def test_kitti_full_size_batch_properties():
     """BASELINE config 4 at full size: 4096 KITTI-shaped images (2048 stereo pairs, 1241x376, 2000 features) in one device
     batch per camera.  The batch is 16 distinct pairs repeated in a scrambled order: every frame must give exactly what its
