@@ -77,7 +77,7 @@ def table(src, dst, frames):
             ("xu%", "sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active"), ("lsu%", "sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active"),
             ("dram%", "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed"), ("warps%", "sm__warps_active.avg.pct_of_peak_sustained_active"),
             ("regs", "launch__registers_per_thread"), ("winst", "smsp__inst_executed.sum")]
-    stage_of = {"k_pyramid_copy0": "pyramid", "k_pyramid_level": "pyramid", "k_pyramid_borders": "pyramid", "k_fast_stream": "fast",
+    stage_of = {"k_pyramid_copy0": "pyramid", "k_pyramid_level": "pyramid", "k_pyramid_borders": "pyramid", "k_pyramid_fringe": "pyramid", "k_fast_stream": "fast",
                 "k_fast_nms": "fast", "k_fast_cells_list": "fast", "k_blur7": "blur", "k_quadtree": "quadtree", "k_assemble": "assemble",
                 "k_orient_describe": "orient_describe", "k_stereo_bucket": "stereo", "k_stereo_match": "stereo", "k_stereo_median": "stereo"}
     seen, traffic, times = {}, collections.OrderedDict(), collections.OrderedDict()
