@@ -123,13 +123,14 @@ int orc_bow_transform(const orc_vocabulary* voc, const uint8_t* features, int n,
 }
 
 /* ORBmatcher::SearchByBoW(KeyFrame* pKF, Frame &F, vector<MapPoint*>&), src/ORBmatcher.cc:269-470, the F.Nleft == -1 path, with
- * ComputeThreeMaxima (:2545-2586).  The feature vectors are the (nodes, starts, feats) arrays of orc_bow_transform.
+ * ComputeThreeMaxima (:2545-2586); kf_kf selects SearchByBoW(KeyFrame*, KeyFrame*, vpMatches12) (:823-963, NLeft == -1): candidates
+ * need a map point too and the threshold is strict.  The feature vectors are the (nodes, starts, feats) arrays of orc_bow_transform.
  * match_f[i] = keyframe row whose map point lands in vpMapPointMatches[i], or -1; kf_out (optional): per keyframe row the scan's
  * best1/best2/idx and accepted (1 kept, 2 removed by the rotation histogram).  Returns nmatches. */
 int orc_search_by_bow(const uint8_t* desc_kf, const orc_keypoint* kps_kf, int n_kf, const int32_t* nodes_kf, const int32_t* starts_kf, const int32_t* feats_kf,
                       int nfv_kf, const uint8_t* has_map_point, const uint8_t* desc_f, const orc_keypoint* kps_f, int n_f, const int32_t* nodes_f,
-                      const int32_t* starts_f, const int32_t* feats_f, int nfv_f, int th_low, float nnratio, int check_orientation, int32_t* match_f,
-                      orc_match* kf_out) {
+                      const int32_t* starts_f, const int32_t* feats_f, int nfv_f, const uint8_t* has_map_point_f, int th_low, float nnratio,
+                      int check_orientation, int kf_kf, int32_t* match_f, orc_match* kf_out) {
     const int HISTO_LENGTH = 30;
     for (int i = 0; i < n_f; i++) match_f[i] = -1;
     if (kf_out) for (int i = 0; i < n_kf; i++) { kf_out[i].best1 = 256; kf_out[i].best2 = 256; kf_out[i].idx = -1; kf_out[i].accepted = 0; }
@@ -147,12 +148,13 @@ int orc_search_by_bow(const uint8_t* desc_kf, const orc_keypoint* kps_kf, int n_
                 for (int iF = starts_f[Fit]; iF < starts_f[Fit + 1]; iF++) {
                     const int realIdxF = feats_f[iF];
                     if (match_f[realIdxF] >= 0) continue;
+                    if (kf_kf && has_map_point_f && !has_map_point_f[realIdxF]) continue;   /* :886-892 (keyframe-keyframe overload) */
                     const int dist = orc_descriptor_distance(dKF, desc_f + (size_t)realIdxF * 32);
                     if (dist < bestDist1) { bestDist2 = bestDist1; bestDist1 = dist; bestIdxF = realIdxF; }
                     else if (dist < bestDist2) { bestDist2 = dist; }
                 }
                 bool ok = false;
-                if (bestDist1 <= th_low && static_cast<float>(bestDist1) < nnratio * static_cast<float>(bestDist2)) {
+                if ((kf_kf ? bestDist1 < th_low : bestDist1 <= th_low) && static_cast<float>(bestDist1) < nnratio * static_cast<float>(bestDist2)) {
                     ok = true;
                     match_f[bestIdxF] = realIdxKF;
                     if (check_orientation) {

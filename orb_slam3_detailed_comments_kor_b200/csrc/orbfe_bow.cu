@@ -212,7 +212,7 @@ struct SbSmem {
 __global__ void __launch_bounds__(SB_NT) k_search_by_bow(int maxF, const int* __restrict__ pairKf, const int* __restrict__ pairF, const uint4* __restrict__ desc,
                                                          const orbfe_keypoint* __restrict__ kps, int rowStride, const int* __restrict__ fvNodes,
                                                          const int* __restrict__ fvStarts, const int* __restrict__ fvFeats, const int* __restrict__ fvCount,
-                                                         const uint8_t* __restrict__ hasMp, int thLow, float nnratio, int checkOri, int* __restrict__ matchF,
+                                                         const uint8_t* __restrict__ hasMp, int thLow, float nnratio, int checkOri, int kfkf, int* __restrict__ matchF,
                                                          orbfe_match* __restrict__ kfOut, int* __restrict__ nmatches) {
     __shared__ SbSmem s;
     const int tid = threadIdx.x, pr = blockIdx.x;
@@ -229,6 +229,8 @@ __global__ void __launch_bounds__(SB_NT) k_search_by_bow(int maxF, const int* __
     for (int i = tid; i < rowStride; i += SB_NT) { mF[i] = -1; if (ko) { orbfe_match m; m.best1 = 256; m.best2 = 256; m.idx = -1; m.accepted = 0; ko[i] = m; } }
     for (int i = tid; i < BOW_MAXF / 4; i += SB_NT) { s.taken[i] = 0; s.state[i] = 0; }
     __syncthreads();
+    if (kfkf && hasMp)   /* keyframe-keyframe variant: rows of the second keyframe without a map point are never candidates (:886-892) */
+        for (int i = tid; i < min(rowStride, BOW_MAXF); i += SB_NT) takenB[i] = hasMp[(size_t)b * rowStride + i] ? 0 : 1;
     /* the node of every query, and that node's run in the frame's feature vector (the lockstep walk of :290-420 is a merge join) */
     for (int e = tid; e < nnA; e += SB_NT) {
         const int node = nodesA[e];
@@ -279,7 +281,7 @@ __global__ void __launch_bounds__(SB_NT) k_search_by_bow(int maxF, const int* __
                 if (bow_ham(qa, qb, __ldg(descB + 2 * row), __ldg(descB + 2 * row + 1)) <= best2) blocked = true;
             }
             if (blocked) { pending++; continue; }
-            const bool ok = bestIdx >= 0 && best1 <= thLow && (float)best1 < nnratio * (float)best2;
+            const bool ok = bestIdx >= 0 && (kfkf ? best1 < thLow : best1 <= thLow) && (float)best1 < nnratio * (float)best2;
             stateB[q] = 1;
             if (ko) { orbfe_match m; m.best1 = best1; m.best2 = best2; m.idx = bestIdx; m.accepted = ok ? 1 : 0; ko[rowA] = m; }
             if (ok) {
@@ -492,7 +494,7 @@ int orbfe_bow_device_views(orbfe_vocabulary* v, const int32_t** d_feat_word, con
 
 int orbfe_search_by_bow_device(int device, int npairs, int max_features, const int32_t* d_pair_kf, const int32_t* d_pair_f, const uint8_t* d_desc,
                                const orbfe_keypoint* d_kps, int row_stride, const int32_t* d_fv_nodes, const int32_t* d_fv_starts, const int32_t* d_fv_feats,
-                               const int32_t* d_fv_count, const uint8_t* d_has_map_point, int th_low, float nnratio, int check_orientation,
+                               const int32_t* d_fv_count, const uint8_t* d_has_map_point, int th_low, float nnratio, int check_orientation, int kf_kf,
                                int32_t* d_match_f, orbfe_match* d_kf_out, int32_t* d_nmatches, void* stream) {
     if (npairs < 1 || !d_pair_kf || !d_pair_f || !d_desc || !d_fv_nodes || !d_fv_starts || !d_fv_feats || !d_fv_count || !d_match_f || row_stride < 1 ||
         (check_orientation && !d_kps)) { orbfe_set_error("bad argument"); return ORBFE_E_INVALID; }
@@ -500,7 +502,7 @@ int orbfe_search_by_bow_device(int device, int npairs, int max_features, const i
     if ((uintptr_t)d_desc & 15) { orbfe_set_error("descriptor array must be 16-byte aligned"); return ORBFE_E_INVALID; }
     ORBFE_CUDA(cudaSetDevice(device));
     k_search_by_bow<<<npairs, SB_NT, 0, (cudaStream_t)stream>>>(max_features, d_pair_kf, d_pair_f, (const uint4*)d_desc, d_kps, row_stride, d_fv_nodes, d_fv_starts,
-                                                                d_fv_feats, d_fv_count, d_has_map_point, th_low, nnratio, check_orientation ? 1 : 0, d_match_f,
+                                                                d_fv_feats, d_fv_count, d_has_map_point, th_low, nnratio, check_orientation ? 1 : 0, kf_kf ? 1 : 0, d_match_f,
                                                                 d_kf_out, d_nmatches);
     ORBFE_CUDA(cudaGetLastError());
     return ORBFE_OK;
@@ -509,8 +511,8 @@ int orbfe_search_by_bow_device(int device, int npairs, int max_features, const i
 /* one (keyframe, frame) pair over host memory: the feature vectors are the fv_* arrays orbfe_bow_result returns */
 int orbfe_search_by_bow(int device, const uint8_t* desc_kf, const orbfe_keypoint* kps_kf, int n_kf, const int32_t* fv_nodes_kf, const int32_t* fv_starts_kf,
                         const int32_t* fv_feats_kf, int nfv_kf, const uint8_t* has_map_point, const uint8_t* desc_f, const orbfe_keypoint* kps_f, int n_f,
-                        const int32_t* fv_nodes_f, const int32_t* fv_starts_f, const int32_t* fv_feats_f, int nfv_f, int th_low, float nnratio,
-                        int check_orientation, int32_t* match_f, orbfe_match* kf_out, int* nmatches) {
+                        const int32_t* fv_nodes_f, const int32_t* fv_starts_f, const int32_t* fv_feats_f, int nfv_f, const uint8_t* has_map_point_f,
+                        int th_low, float nnratio, int check_orientation, int kf_kf, int32_t* match_f, orbfe_match* kf_out, int* nmatches) {
     if (n_kf < 0 || n_f < 0 || nfv_kf < 0 || nfv_f < 0 || !match_f || (n_kf && !desc_kf) || (n_f && !desc_f) || (check_orientation && (!kps_kf || !kps_f)) ||
         (nfv_kf && (!fv_nodes_kf || !fv_starts_kf || !fv_feats_kf)) || (nfv_f && (!fv_nodes_f || !fv_starts_f || !fv_feats_f))) { orbfe_set_error("bad argument"); return ORBFE_E_INVALID; }
     const int S = std::max(std::max(n_kf, n_f), 1);
@@ -532,6 +534,7 @@ int orbfe_search_by_bow(int device, const uint8_t* desc_kf, const orbfe_keypoint
     if (kps_kf && n_kf) memcpy(hKps.data(), kps_kf, (size_t)n_kf * sizeof(orbfe_keypoint));
     if (kps_f && n_f) memcpy(hKps.data() + S, kps_f, (size_t)n_f * sizeof(orbfe_keypoint));
     if (has_map_point && n_kf) memcpy(hMp.data(), has_map_point, (size_t)n_kf);
+    if (has_map_point_f && n_f) memcpy(hMp.data() + S, has_map_point_f, (size_t)n_f);
     if (nfv_kf > S || nfv_f > S) { orbfe_set_error("feature vector longer than the frame"); return ORBFE_E_INVALID; }
     if (nfv_kf) {
         if (fv_starts_kf[nfv_kf] > S) { orbfe_set_error("feature vector longer than the frame"); return ORBFE_E_INVALID; }
@@ -560,7 +563,7 @@ int orbfe_search_by_bow(int device, const uint8_t* desc_kf, const orbfe_keypoint
     if (e == cudaSuccess)
         rc = orbfe_search_by_bow_device(device, 1, S, (const int32_t*)(d + oPair), (const int32_t*)(d + oPair) + 1, d + oDesc, (const orbfe_keypoint*)(d + oKps), S,
                                         (const int32_t*)(d + oNodes), (const int32_t*)(d + oStarts), (const int32_t*)(d + oFeats), (const int32_t*)(d + oCount),
-                                        d + oMp, th_low, nnratio, check_orientation, (int32_t*)(d + oMatch), (orbfe_match*)(d + oKf), (int32_t*)(d + oNm), nullptr);
+                                        d + oMp, th_low, nnratio, check_orientation, kf_kf, (int32_t*)(d + oMatch), (orbfe_match*)(d + oKf), (int32_t*)(d + oNm), nullptr);
     if (rc == ORBFE_OK && e == cudaSuccess) e = cudaDeviceSynchronize();
     if (rc == ORBFE_OK && e == cudaSuccess && n_f) e = cudaMemcpy(match_f, d + oMatch, (size_t)n_f * 4, cudaMemcpyDeviceToHost);
     if (rc == ORBFE_OK && e == cudaSuccess && kf_out && n_kf) e = cudaMemcpy(kf_out, d + oKf, (size_t)n_kf * sizeof(orbfe_match), cudaMemcpyDeviceToHost);
