@@ -279,6 +279,9 @@ typedef struct orbfe_frame_grid {   /* Frame::mnMinX, mnMinY, mfGridElementWidth
 #define ORBFE_PQ_AFTER_LEFT 8  /* right-camera half (:145-211) of the map point of the query before: not run when that one
                                   failed the ratio test (the `continue` at :117-118 leaves the whole iteration) */
 #define ORBFE_PQ_BEST_ONLY 16  /* frame-to-frame rule (:2267-2300): accepted iff bestDist <= TH_HIGH, no second-best test */
+#define ORBFE_PQ_ERROR_GATE 64  /* ORBmatcher::Fuse (:1643-1841): a candidate is skipped when its reprojection error fails the chi-square
+                                  test — (ex^2+ey^2+er^2)*mvInvLevelSigma2[octave] > 7.8 if mvuRight[row] >= 0 (er = xr - mvuRight[row]), else
+                                  (ex^2+ey^2)*mvInvLevelSigma2[octave] > 5.99 (:1714-1740) — instead of the |xr - mvuRight| gate */
 #define ORBFE_PQ_NEEDS_LEFT_WINDOW 32 /* right-camera half (:2325-2386) of the query before: not run when that one's window holds
                                   no keypoint (`if(vIndices2.empty()) continue;` at :2262-2263) */
 typedef struct orbfe_proj_query {   /* one (map point, camera) search, in the reference's loop order */
@@ -316,19 +319,22 @@ typedef struct orbfe_proj_match {
  *     -1, or NULL;   d_taken_in: per row, nonzero iff F.mvpMapPoints[row] has observations (NULL: none);
  *   d_queries / d_qdesc (pMP->GetDescriptor()): frame f = entries [d_q_offsets[f], d_q_offsets[f+1]);
  *   th_high = ORBmatcher::TH_HIGH (100), nnratio = mfNNratio;   d_taken_out (may be NULL or d_taken_in): occupancy afterwards;
+ *   d_inv_level_sigma2: mvInvLevelSigma2 (16 floats, one per pyramid level), read for ORBFE_PQ_ERROR_GATE queries (else may be NULL).
+ *     ORBmatcher::Fuse(pKF, vpMapPoints, th, bRight) is: ORBFE_PQ_BEST_ONLY | ORBFE_PQ_ERROR_GATE queries without ORBFE_PQ_BLOCKS,
+ *     th_high = TH_LOW, no d_taken_in; best_idx of an accepted query is the keypoint to fuse with or to add the observation to;
  *   check_orientation != 0: after the searches, the rotation histogram of (query angle - keypoint angle) over the frame's matches
  *     (30 bins, ComputeThreeMaxima, src/ORBmatcher.cc:2545-2586) removes the matches outside the three fullest bins. */
 int orbfe_search_by_projection_device(int device, int nframes, int max_keypoints, const orbfe_keypoint* d_kps, const uint8_t* d_desc,
                                       const int32_t* d_kp_offsets, const int32_t* d_n_left, const float* d_u_right, const int32_t* d_partner,
                                       const uint8_t* d_taken_in, const orbfe_frame_grid* d_grids, const orbfe_proj_query* d_queries,
                                       const uint8_t* d_qdesc, const int32_t* d_q_offsets, int th_high, float nnratio, int check_orientation,
-                                      orbfe_proj_match* d_out, uint8_t* d_taken_out, void* stream);
+                                      const float* d_inv_level_sigma2, orbfe_proj_match* d_out, uint8_t* d_taken_out, void* stream);
 /* One frame over host memory (copies inside, synchronous).  taken is updated in place (may be NULL); *nmatches receives the
  * reference's return value (an accepted row with a stereo partner counts twice). */
 int orbfe_search_by_projection(int device, const orbfe_keypoint* kps, const uint8_t* desc, int n, int n_left, const float* u_right,
                                const int32_t* partner, uint8_t* taken, const orbfe_frame_grid* grid, const orbfe_proj_query* queries,
-                               const uint8_t* qdesc, int nq, int th_high, float nnratio, int check_orientation, orbfe_proj_match* out,
-                               int* nmatches);
+                               const uint8_t* qdesc, int nq, int th_high, float nnratio, int check_orientation,
+                               const float* inv_level_sigma2, orbfe_proj_match* out, int* nmatches);
 
 /* ------------------------------------------------------------------------------------------ input conditioning */
 /* The steps the example drivers and Tracking run on each image before the extractor, so that an

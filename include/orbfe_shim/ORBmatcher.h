@@ -97,7 +97,8 @@ inline int SearchByProjection(const std::vector<cv::KeyPoint>& keys, const cv::M
                               const std::vector<int>* partner, std::vector<unsigned char>& taken, float mnMinX, float mnMinY,
                               float mfGridElementWidthInv, float mfGridElementHeightInv, const std::vector<orbfe_proj_query>& queries,
                               const cv::Mat& queryDescriptors, float mfNNratio, std::vector<orbfe_proj_match>& out, bool checkOrientation = false,
-                              int device = 0) {
+                              int device = 0, const float* invLevelSigma2 = nullptr /* mvInvLevelSigma2 (16 entries) for ORBFE_PQ_ERROR_GATE queries (Fuse) */,
+                              int thHigh = 100 /* TH_HIGH; Fuse passes TH_LOW */) {
     static_assert(sizeof(cv::KeyPoint) == sizeof(orbfe_keypoint), "cv::KeyPoint layout");
     const int n = (int)keys.size(), nq = (int)queries.size();
     out.resize(nq);
@@ -108,8 +109,8 @@ inline int SearchByProjection(const std::vector<cv::KeyPoint>& keys, const cv::M
     const orbfe_frame_grid grid = {mnMinX, mnMinY, mfGridElementWidthInv, mfGridElementHeightInv};
     int nmatches = 0;
     if (orbfe_search_by_projection(device, reinterpret_cast<const orbfe_keypoint*>(keys.data()), d.data(), n, Nleft, uRight ? uRight->data() : nullptr,
-                                   partner ? partner->data() : nullptr, taken.data(), &grid, queries.data(), qd.data(), nq, ORBmatcher::TH_HIGH,
-                                   mfNNratio, checkOrientation ? 1 : 0, out.data(), &nmatches) != ORBFE_OK)
+                                   partner ? partner->data() : nullptr, taken.data(), &grid, queries.data(), qd.data(), nq, thHigh,
+                                   mfNNratio, checkOrientation ? 1 : 0, invLevelSigma2, out.data(), &nmatches) != ORBFE_OK)
         throw std::runtime_error(std::string("orbfe_search_by_projection: ") + orbfe_last_error());
     return nmatches;
 }

@@ -70,7 +70,7 @@ def lib():
     L.orc_search_by_bow.argtypes = [vp, vp, C.c_int, vp, vp, vp, C.c_int, vp, vp, vp, C.c_int, vp, vp, vp, C.c_int, vp, C.c_int, C.c_float, C.c_int, C.c_int, vp, vp]
     L.orc_search_by_bow.restype = C.c_int
     L.orc_distinctive_descriptors.argtypes = [vp, vp, C.c_int, vp, vp]
-    L.orc_search_by_projection.argtypes = [vp, vp, C.c_int, C.c_int, vp, vp, vp, vp, vp, vp, C.c_int, C.c_int, C.c_float, C.c_int, vp]
+    L.orc_search_by_projection.argtypes = [vp, vp, C.c_int, C.c_int, vp, vp, vp, vp, vp, vp, C.c_int, C.c_int, C.c_float, C.c_int, vp, vp]
     L.orc_search_by_projection.restype = C.c_int
     L.orc_clahe_u8.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_double, C.c_int, C.c_int, vp, C.c_int, vp]
     L.orc_clahe_u8.restype = C.c_int
@@ -304,8 +304,8 @@ PROJ_MATCH_DTYPE = np.dtype([("best_idx", "<i4"), ("best_dist", "<i4"), ("best_l
 
 
 def search_by_projection(kps, desc, queries, qdesc, grid, n_left=-1, u_right=None, partner=None, taken=None, th_high=100, nnratio=0.8,
-                         check_orientation=False):
-    """ORBmatcher::SearchByProjection(Frame&, vpMapPoints, th) / (CurrentFrame, LastFrame, th, bMono) on arrays, serial.
+                         check_orientation=False, inv_level_sigma2=None):
+    """ORBmatcher::SearchByProjection(Frame&, vpMapPoints, th) / (CurrentFrame, LastFrame, th, bMono) / Fuse on arrays, serial.
     Returns (matches, taken_after, nmatches)."""
     kps = np.ascontiguousarray(kps, KP_DTYPE)
     desc = np.ascontiguousarray(desc, np.uint8)
@@ -316,9 +316,10 @@ def search_by_projection(kps, desc, queries, qdesc, grid, n_left=-1, u_right=Non
     pt = None if partner is None else np.ascontiguousarray(partner, np.int32)
     tk = np.zeros(kps.shape[0], np.uint8) if taken is None else np.array(taken, np.uint8)
     out = np.zeros(queries.shape[0], PROJ_MATCH_DTYPE)
+    sig = None if inv_level_sigma2 is None else np.ascontiguousarray(np.resize(np.asarray(inv_level_sigma2, np.float32), 16))
     nm = lib().orc_search_by_projection(_ptr(kps), _ptr(desc), kps.shape[0], n_left, _ptr(ur) if ur is not None else None,
                                         _ptr(pt) if pt is not None else None, _ptr(tk), _ptr(grid), _ptr(queries), _ptr(qdesc),
-                                        queries.shape[0], th_high, nnratio, int(check_orientation), _ptr(out))
+                                        queries.shape[0], th_high, nnratio, int(check_orientation), _ptr(sig) if sig is not None else None, _ptr(out))
     return out, tk, nm
 
 

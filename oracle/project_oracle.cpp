@@ -6,6 +6,7 @@
  *   /root/reference/src/ORBmatcher.cc:44-214 ORBmatcher::SearchByProjection(Frame&, const vector<MapPoint*>&, th, ...)
  *   /root/reference/src/ORBmatcher.cc:2193-2419 ORBmatcher::SearchByProjection(Frame &CurrentFrame, const Frame &LastFrame, th, bMono)
  *   /root/reference/src/ORBmatcher.cc:2545-2586 ORBmatcher::ComputeThreeMaxima
+ *   /root/reference/src/ORBmatcher.cc:1643-1841 ORBmatcher::Fuse(pKF, vpMapPoints, th, bRight): the search (PQ_ERROR_GATE queries)
  * on plain arrays, in the reference's serial order (a map point that was matched blocks its keypoint for the map points
  * after it).  No third-party arithmetic is involved; parity unpinned beyond the independent Python restatement in
  * tools/make_goldens.py (tests/golden/projection.npz). */
@@ -31,7 +32,7 @@ typedef struct { float min_x, min_y, inv_w, inv_h; } orc_frame_grid;
 typedef struct { float x, y, radius, xr; int32_t min_level, max_level, flags; float angle; } orc_proj_query;
 typedef struct { int32_t best_idx, best_dist, best_level, second_dist, second_level, accepted, status; } orc_proj_match;
 
-enum { PQ_RIGHT = 1, PQ_BLOCKS = 2, PQ_SKIP = 4, PQ_AFTER_LEFT = 8, PQ_BEST_ONLY = 16, PQ_NEEDS_LEFT_WINDOW = 32 };
+enum { PQ_RIGHT = 1, PQ_BLOCKS = 2, PQ_SKIP = 4, PQ_AFTER_LEFT = 8, PQ_BEST_ONLY = 16, PQ_NEEDS_LEFT_WINDOW = 32, PQ_ERROR_GATE = 64 };
 enum { PS_NO_CANDIDATES = 0, PS_ACCEPTED = 1, PS_OVER_THRESHOLD = 2, PS_RATIO_REJECTED = 3, PS_SKIPPED = 4, PS_DROPPED = 6, PS_ROTATION = 7, PS_EMPTY_WINDOW = 8 };
 const int HISTO_LENGTH = 30; /* ORBmatcher.cc:38 */
 
@@ -40,7 +41,7 @@ const int HISTO_LENGTH = 30; /* ORBmatcher.cc:38 */
  * Returns nmatches as the reference counts them (a matched row with a partner counts twice). */
 int orc_search_by_projection(const orc_keypoint* kps, const uint8_t* desc, int n, int n_left, const float* u_right, const int32_t* partner,
                              uint8_t* taken, const orc_frame_grid* g, const orc_proj_query* q, const uint8_t* qdesc, int nq, int th_high,
-                             float nnratio, int check_orientation, orc_proj_match* out) {
+                             float nnratio, int check_orientation, const float* inv_level_sigma2, orc_proj_match* out) {
     Grid* grid = new Grid();
     /* AssignFeaturesToGrid + PosInGrid */
     for (int i = 0; i < n; i++) {
@@ -90,7 +91,18 @@ int orc_search_by_projection(const orc_keypoint* kps, const uint8_t* desc, int n
         int bestDist = 256, bestLevel = -1, bestDist2 = 256, bestLevel2 = -1, bestIdx = -1;
         for (int idx : vIndices) {
             if (taken[idx]) continue;
-            if (n_left < 0 && u_right && u_right[idx] > 0) {
+            if ((p.flags & PQ_ERROR_GATE) && inv_level_sigma2) {          /* ORBmatcher::Fuse, ORBmatcher.cc:1714-1740 */
+                const float kpx = kps[idx].x, kpy = kps[idx].y;
+                const float ex = p.x - kpx, ey = p.y - kpy;
+                if (u_right && u_right[idx] >= 0) {
+                    const float er = p.xr - u_right[idx];
+                    const float e2 = ex * ex + ey * ey + er * er;
+                    if (e2 * inv_level_sigma2[kps[idx].octave] > 7.8) continue;
+                } else {
+                    const float e2 = ex * ex + ey * ey;
+                    if (e2 * inv_level_sigma2[kps[idx].octave] > 5.99) continue;
+                }
+            } else if (n_left < 0 && u_right && u_right[idx] > 0) {
                 const float er = std::fabs(p.xr - u_right[idx]);
                 if (er > r) continue;
             }

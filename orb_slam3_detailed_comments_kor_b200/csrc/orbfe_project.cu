@@ -48,7 +48,30 @@ struct PjFrame {
     const int32_t* partner;
     int n, nLeft;
     float minx, miny, invw, invh;
+    const float* invSigma2;
 };
+
+/* the per-candidate gate on mvuRight: |xr - mvuRight| <= radius for the SearchByProjection overloads (rectified rigs only), the
+ * chi-square reprojection test of ORBmatcher::Fuse for ORBFE_PQ_ERROR_GATE queries.  true = the candidate is skipped. */
+static __device__ __forceinline__ bool pj_gated(const PjFrame& fr, const orbfe_proj_query& p, int row, int oct, bool gateRight) {
+    if ((p.flags & ORBFE_PQ_ERROR_GATE) && fr.invSigma2) {
+        const float ex = __fsub_rn(p.x, __ldg(&fr.kps[row].x)), ey = __fsub_rn(p.y, __ldg(&fr.kps[row].y));
+        const float is2 = __ldg(fr.invSigma2 + oct);
+        const float ur = fr.uRight ? __ldg(fr.uRight + row) : -1.0f;
+        if (ur >= 0) {
+            const float er = __fsub_rn(p.xr, ur);
+            const float e2 = __fadd_rn(__fadd_rn(__fmul_rn(ex, ex), __fmul_rn(ey, ey)), __fmul_rn(er, er));
+            return (double)__fmul_rn(e2, is2) > 7.8;
+        }
+        const float e2 = __fadd_rn(__fmul_rn(ex, ex), __fmul_rn(ey, ey));
+        return (double)__fmul_rn(e2, is2) > 5.99;
+    }
+    if (gateRight) {
+        const float ur = __ldg(fr.uRight + row);
+        if (ur > 0 && fabsf(p.xr - ur) > p.radius) return true;
+    }
+    return false;
+}
 
 static __device__ __forceinline__ int pj_ham(const uint4 qa, const uint4 qb, const uint4 a, const uint4 b) {
     return __popc(qa.x ^ a.x) + __popc(qa.y ^ a.y) + __popc(qa.z ^ a.z) + __popc(qa.w ^ a.w) + __popc(qb.x ^ b.x) + __popc(qb.y ^ b.y) +
@@ -88,7 +111,7 @@ __global__ void __launch_bounds__(PJ_NT) k_search_by_projection(int maxKp, const
                                                                 const uint8_t* __restrict__ takenIn, const orbfe_frame_grid* __restrict__ grids,
                                                                 const orbfe_proj_query* __restrict__ queries, const uint8_t* __restrict__ qdescAll,
                                                                 const int32_t* __restrict__ qOff, int thHigh, float nnratio, int checkOri,
-                                                                orbfe_proj_match* out, uint8_t* __restrict__ takenOut) {
+                                                                const float* __restrict__ invSigma2, orbfe_proj_match* out, uint8_t* __restrict__ takenOut) {
     extern __shared__ __align__(16) unsigned char pj_raw[];
     PjSmem& s = *reinterpret_cast<PjSmem*>(pj_raw);
     const int tid = threadIdx.x, f = blockIdx.x;
@@ -102,6 +125,7 @@ __global__ void __launch_bounds__(PJ_NT) k_search_by_projection(int maxKp, const
     fr.nLeft = nLeftAll ? nLeftAll[f] : -1;
     const orbfe_frame_grid g = grids[f];
     fr.minx = g.min_x; fr.miny = g.min_y; fr.invw = g.inv_w; fr.invh = g.inv_h;
+    fr.invSigma2 = invSigma2;
     const orbfe_proj_query* qs = queries + q0;
     const uint4* qdesc = reinterpret_cast<const uint4*>(qdescAll) + (size_t)q0 * 2;
     orbfe_proj_match* res = out + q0;
@@ -192,12 +216,9 @@ __global__ void __launch_bounds__(PJ_NT) k_search_by_projection(int maxKp, const
             const orbfe_proj_query p = qs[q];
             if (p.flags & (ORBFE_PQ_AFTER_LEFT | ORBFE_PQ_NEEDS_LEFT_WINDOW))
                 res[q].accepted = (q > 0 && status[(q - 1) * 7] == PJ_PENDING) ? 0 : 1;   /* may I look at q-1 in step B? */
-            pj_window(fr, s, p, [&](int row, int) {
+            pj_window(fr, s, p, [&](int row, int oct) {
                 if (takenB[row] & 1) return;
-                if (gateRight) {
-                    const float ur = __ldg(fr.uRight + row);
-                    if (ur > 0 && fabsf(p.xr - ur) > p.radius) return;
-                }
+                if (pj_gated(fr, p, row, oct, gateRight)) return;
                 atomicMin(&s.owner[row], q);
                 if (stereoRig) {
                     const int pt = __ldg(fr.partner + row);
@@ -226,10 +247,7 @@ __global__ void __launch_bounds__(PJ_NT) k_search_by_projection(int maxKp, const
             pj_window(fr, s, p, [&](int row, int oct) {
                 seen++;
                 if (takenB[row] & 1) return;
-                if (gateRight) {
-                    const float ur = __ldg(fr.uRight + row);
-                    if (ur > 0 && fabsf(p.xr - ur) > p.radius) return;
-                }
+                if (pj_gated(fr, p, row, oct, gateRight)) return;
                 const int dist = pj_ham(qa, qb, __ldg(fr.desc + 2 * row), __ldg(fr.desc + 2 * row + 1));
                 if (dist < bestDist) { bestDist2 = bestDist; bestDist = dist; bestLevel2 = bestLevel; bestLevel = oct; bestIdx = row; }
                 else if (dist < bestDist2) { bestLevel2 = oct; bestDist2 = dist; }
@@ -242,12 +260,9 @@ __global__ void __launch_bounds__(PJ_NT) k_search_by_projection(int maxKp, const
                 st = bestDist > thHigh ? ORBFE_PS_OVER_THRESHOLD
                      : (!bestOnly && bestLevel == bestLevel2 && (float)bestDist > nnratio * (float)bestDist2) ? ORBFE_PS_RATIO_REJECTED : ORBFE_PS_ACCEPTED;
                 const int reach = bestDist2;   /* candidates above it cannot change any reported field */
-                pj_window(fr, s, p, [&](int row, int) {
+                pj_window(fr, s, p, [&](int row, int oct) {
                     if (blocked || (takenB[row] & 1)) return;
-                    if (gateRight) {
-                        const float ur = __ldg(fr.uRight + row);
-                        if (ur > 0 && fabsf(p.xr - ur) > p.radius) return;
-                    }
+                    if (pj_gated(fr, p, row, oct, gateRight)) return;
                     if (s.owner[row] < q && pj_ham(qa, qb, __ldg(fr.desc + 2 * row), __ldg(fr.desc + 2 * row + 1)) <= reach) blocked = true;
                 });
                 if (st == ORBFE_PS_ACCEPTED && stereoRig) {
@@ -320,7 +335,7 @@ int orbfe_search_by_projection_device(int device, int nframes, int max_keypoints
                                       const int32_t* d_kp_offsets, const int32_t* d_n_left, const float* d_u_right, const int32_t* d_partner,
                                       const uint8_t* d_taken_in, const orbfe_frame_grid* d_grids, const orbfe_proj_query* d_queries,
                                       const uint8_t* d_qdesc, const int32_t* d_q_offsets, int th_high, float nnratio, int check_orientation,
-                                      orbfe_proj_match* d_out, uint8_t* d_taken_out, void* stream) {
+                                      const float* d_inv_level_sigma2, orbfe_proj_match* d_out, uint8_t* d_taken_out, void* stream) {
     if (nframes < 1 || !d_kps || !d_desc || !d_kp_offsets || !d_grids || !d_queries || !d_qdesc || !d_q_offsets || !d_out) { orbfe_set_error("bad argument"); return ORBFE_E_INVALID; }
     if (max_keypoints < 0 || max_keypoints > PJ_MAXKP) { orbfe_set_error("at most %d keypoints per frame (both cameras together)", PJ_MAXKP); return ORBFE_E_CAPACITY; }
     if (((uintptr_t)d_desc | (uintptr_t)d_qdesc) & 15) { orbfe_set_error("descriptor arrays must be 16-byte aligned"); return ORBFE_E_INVALID; }
@@ -332,14 +347,14 @@ int orbfe_search_by_projection_device(int device, int nframes, int max_keypoints
     }
     k_search_by_projection<<<nframes, PJ_NT, sizeof(PjSmem), (cudaStream_t)stream>>>(max_keypoints, d_kps, d_desc, d_kp_offsets, d_n_left, d_u_right, d_partner,
                                                                                     d_taken_in, d_grids, d_queries, d_qdesc, d_q_offsets, th_high, nnratio,
-                                                                                    check_orientation ? 1 : 0, d_out, d_taken_out);
+                                                                                    check_orientation ? 1 : 0, d_inv_level_sigma2, d_out, d_taken_out);
     ORBFE_CUDA(cudaGetLastError());
     return ORBFE_OK;
 }
 
 int orbfe_search_by_projection(int device, const orbfe_keypoint* kps, const uint8_t* desc, int n, int n_left, const float* u_right, const int32_t* partner,
                                uint8_t* taken, const orbfe_frame_grid* grid, const orbfe_proj_query* queries, const uint8_t* qdesc, int nq, int th_high,
-                               float nnratio, int check_orientation, orbfe_proj_match* out, int* nmatches) {
+                               float nnratio, int check_orientation, const float* inv_level_sigma2, orbfe_proj_match* out, int* nmatches) {
     if (!kps || !desc || !grid || !queries || !qdesc || !out || n < 0 || nq < 0) { orbfe_set_error("bad argument"); return ORBFE_E_INVALID; }
     if (n > PJ_MAXKP) { orbfe_set_error("at most %d keypoints per frame (both cameras together)", PJ_MAXKP); return ORBFE_E_CAPACITY; }
     if (nmatches) *nmatches = 0;
@@ -356,6 +371,9 @@ int orbfe_search_by_projection(int device, const orbfe_keypoint* kps, const uint
     const size_t oKps = take((size_t)n * sizeof(orbfe_keypoint)), oDesc = take((size_t)n * 32), oQd = take((size_t)nq * 32);
     const size_t oQ = take((size_t)nq * sizeof(orbfe_proj_query)), oOut = take((size_t)nq * sizeof(orbfe_proj_match));
     const size_t oUr = take((size_t)n * 4), oPt = take((size_t)n * 4), oTk = take((size_t)n), oGrid = take(sizeof(orbfe_frame_grid)), oOff = take(5 * sizeof(int32_t));
+    const size_t oSig = take(16 * sizeof(float));
+    for (int i = 0; i < nq; i++)
+        if ((queries[i].flags & ORBFE_PQ_ERROR_GATE) && !inv_level_sigma2) { orbfe_set_error("ORBFE_PQ_ERROR_GATE needs inv_level_sigma2"); return ORBFE_E_INVALID; }
     uint8_t* d = nullptr;
     ORBFE_CUDA(cudaMalloc((void**)&d, off));
     cudaStream_t st = nullptr;
@@ -371,6 +389,7 @@ int orbfe_search_by_projection(int device, const orbfe_keypoint* kps, const uint
     if (taken) PJ_UP(oTk, taken, (size_t)n);
     PJ_UP(oGrid, grid, sizeof(orbfe_frame_grid));
     PJ_UP(oOff, offs, sizeof(offs));
+    if (inv_level_sigma2) PJ_UP(oSig, inv_level_sigma2, 16 * sizeof(float));
 #undef PJ_UP
     int rc = ORBFE_OK;
     if (e == cudaSuccess)
@@ -378,7 +397,7 @@ int orbfe_search_by_projection(int device, const orbfe_keypoint* kps, const uint
                                                (const int32_t*)(d + oOff) + 4, u_right ? (const float*)(d + oUr) : nullptr,
                                                partner ? (const int32_t*)(d + oPt) : nullptr, taken ? d + oTk : nullptr, (const orbfe_frame_grid*)(d + oGrid),
                                                (const orbfe_proj_query*)(d + oQ), d + oQd, (const int32_t*)(d + oOff) + 2, th_high, nnratio, check_orientation,
-                                               (orbfe_proj_match*)(d + oOut), taken ? d + oTk : nullptr, st);
+                                               inv_level_sigma2 ? (const float*)(d + oSig) : nullptr, (orbfe_proj_match*)(d + oOut), taken ? d + oTk : nullptr, st);
     if (rc == ORBFE_OK && e == cudaSuccess) e = cudaMemcpyAsync(out, d + oOut, (size_t)nq * sizeof(orbfe_proj_match), cudaMemcpyDeviceToHost, st);
     if (rc == ORBFE_OK && e == cudaSuccess && taken && n > 0) e = cudaMemcpyAsync(taken, d + oTk, (size_t)n, cudaMemcpyDeviceToHost, st);
     if (rc == ORBFE_OK && e == cudaSuccess) e = cudaStreamSynchronize(st);

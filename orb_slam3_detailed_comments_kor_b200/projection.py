@@ -13,7 +13,7 @@ PROJ_QUERY_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("radius", "<f4"), ("xr
                              ("flags", "<i4"), ("angle", "<f4")])
 PROJ_MATCH_DTYPE = np.dtype([("best_idx", "<i4"), ("best_dist", "<i4"), ("best_level", "<i4"), ("second_dist", "<i4"),
                              ("second_level", "<i4"), ("accepted", "<i4"), ("status", "<i4")])
-PQ_RIGHT, PQ_BLOCKS, PQ_SKIP, PQ_AFTER_LEFT, PQ_BEST_ONLY, PQ_NEEDS_LEFT_WINDOW = 1, 2, 4, 8, 16, 32
+PQ_RIGHT, PQ_BLOCKS, PQ_SKIP, PQ_AFTER_LEFT, PQ_BEST_ONLY, PQ_NEEDS_LEFT_WINDOW, PQ_ERROR_GATE = 1, 2, 4, 8, 16, 32, 64
 (PS_NO_CANDIDATES, PS_ACCEPTED, PS_OVER_THRESHOLD, PS_RATIO_REJECTED, PS_SKIPPED, PS_CAPACITY, PS_DROPPED, PS_ROTATION,
  PS_EMPTY_WINDOW) = range(9)
 TH_HIGH = 100   # ORBmatcher.cc:36
@@ -32,7 +32,7 @@ def frame_grid(min_x, max_x, min_y, max_y):
 
 
 def search_by_projection(kps, desc, queries, qdesc, grid, n_left=-1, u_right=None, partner=None, taken=None, th_high=TH_HIGH, nnratio=0.8,
-                         check_orientation=False, device=0):
+                         check_orientation=False, inv_level_sigma2=None, device=0):
     """One frame, host arrays.  Returns (matches[PROJ_MATCH_DTYPE], taken_after u8[n], nmatches)."""
     kps = np.ascontiguousarray(kps, KP_DTYPE)
     desc = np.ascontiguousarray(desc, np.uint8)
@@ -45,19 +45,22 @@ def search_by_projection(kps, desc, queries, qdesc, grid, n_left=-1, u_right=Non
     pt = None if partner is None else np.ascontiguousarray(partner, np.int32)
     tk = np.zeros(n, np.uint8) if taken is None else np.array(taken, np.uint8)
     out = np.zeros(nq, PROJ_MATCH_DTYPE)
+    sig = None if inv_level_sigma2 is None else np.ascontiguousarray(np.resize(np.asarray(inv_level_sigma2, np.float32), 16))
     nm = C.c_int(0)
     check(_lib.lib().orbfe_search_by_projection(device, ptr(kps), ptr(desc), n, n_left, ptr(ur) if ur is not None else None,
                                                 ptr(pt) if pt is not None else None, ptr(tk), ptr(grid), ptr(queries), ptr(qdesc), nq,
-                                                th_high, C.c_float(nnratio), int(check_orientation), ptr(out), C.byref(nm)))
+                                                th_high, C.c_float(nnratio), int(check_orientation), ptr(sig) if sig is not None else None, ptr(out),
+                                                C.byref(nm)))
     return out, tk, nm.value
 
 
 def search_by_projection_device(nframes, max_keypoints, d_kps, d_desc, d_kp_offsets, d_grids, d_queries, d_qdesc, d_q_offsets, d_out,
                                 d_n_left=None, d_u_right=None, d_partner=None, d_taken_in=None, d_taken_out=None, th_high=TH_HIGH,
-                                nnratio=0.8, check_orientation=False, device=0, stream=None):
+                                nnratio=0.8, check_orientation=False, d_inv_level_sigma2=None, device=0, stream=None):
     """A batch of frames, device pointers (ints), asynchronous on `stream`."""
     vp = lambda p: C.c_void_p(p) if p else None  # noqa: E731
     check(_lib.lib().orbfe_search_by_projection_device(device, nframes, max_keypoints, vp(d_kps), vp(d_desc), vp(d_kp_offsets), vp(d_n_left),
                                                        vp(d_u_right), vp(d_partner), vp(d_taken_in), vp(d_grids), vp(d_queries), vp(d_qdesc),
-                                                       vp(d_q_offsets), th_high, C.c_float(nnratio), int(check_orientation), vp(d_out), vp(d_taken_out),
+                                                       vp(d_q_offsets), th_high, C.c_float(nnratio), int(check_orientation), vp(d_inv_level_sigma2), vp(d_out),
+                                                       vp(d_taken_out),
                                                        vp(stream)))

@@ -5,7 +5,7 @@ import numpy as np
 KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"), ("response", "<f4"), ("octave", "<i4"), ("class_id", "<i4")])
 PROJ_QUERY_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("radius", "<f4"), ("xr", "<f4"), ("min_level", "<i4"), ("max_level", "<i4"), ("flags", "<i4"),
                              ("angle", "<f4")])
-PQ_RIGHT, PQ_BLOCKS, PQ_SKIP, PQ_AFTER_LEFT, PQ_BEST_ONLY, PQ_NEEDS_LEFT_WINDOW = 1, 2, 4, 8, 16, 32
+PQ_RIGHT, PQ_BLOCKS, PQ_SKIP, PQ_AFTER_LEFT, PQ_BEST_ONLY, PQ_NEEDS_LEFT_WINDOW, PQ_ERROR_GATE = 1, 2, 4, 8, 16, 32, 64
 
 
 def _flip(rng, d, k):
@@ -15,11 +15,12 @@ def _flip(rng, d, k):
     return d
 
 
-def make_case(seed, n=600, nq=700, W=752, H=480, th=1.0, fisheye=False, stereo_gate=False, crowd=0.0, last_frame=None):
+def make_case(seed, n=600, nq=700, W=752, H=480, th=1.0, fisheye=False, stereo_gate=False, crowd=0.0, last_frame=None, fuse=False):
     """crowd: fraction of the map points aimed at a small set of keypoints (long chains of map points competing for the same
     keypoints); th: the search-window factor of SearchByProjection.  last_frame: None = the SearchLocalPoints overload;
     "still" / "forward" / "backward" = SearchByProjection(CurrentFrame, LastFrame, th, bMono) with the level range of that
-    motion (src/ORBmatcher.cc:2253-2258), best-only acceptance and the rotation check (case["check_orientation"] = 1)."""
+    motion (src/ORBmatcher.cc:2253-2258), best-only acceptance and the rotation check (case["check_orientation"] = 1).
+    fuse: the search of ORBmatcher::Fuse (:1643-1841): best only, TH_LOW, chi-square gate on the reprojection error, nothing blocks."""
     rng = np.random.RandomState(seed)
     f32 = np.float32
     kps = np.zeros(n, KP_DTYPE)
@@ -43,6 +44,10 @@ def make_case(seed, n=600, nq=700, W=752, H=480, th=1.0, fisheye=False, stereo_g
             "grid": np.array([0, 0, f32(64) / f32(W), f32(48) / f32(H)], f32), "th_high": np.array([100], np.int32),
             "nnratio": np.array([0.8], f32), "taken": (rng.uniform(size=n) < 0.08).astype(np.uint8),
             "check_orientation": np.array([1 if last_frame else 0], np.int32)}
+    if fuse:
+        case["th_high"] = np.array([50], np.int32)
+        case["taken"] = np.zeros(n, np.uint8)
+        case["inv_level_sigma2"] = np.array([f32(1) / (f32(1.2) ** i * f32(1.2) ** i) for i in range(16)], f32)
     turn = f32(rng.uniform(-40, 40))                          # camera roll between the two frames (last_frame cases)
     if stereo_gate:
         ur = kps["x"] - rng.uniform(1, 40, n).astype(f32)
@@ -67,8 +72,9 @@ def make_case(seed, n=600, nq=700, W=752, H=480, th=1.0, fisheye=False, stereo_g
             t = int(hot[rng.randint(len(hot))]) if rng.uniform() < crowd else int(rng.randint(n))
             lvl = int(min(7, kps["octave"][t] + rng.randint(0, 2)))
             r = f32(2.5 if rng.uniform() < 0.5 else 4.0) * f32(th) * scale[lvl]
-            x = f32(kps["x"][t] + rng.uniform(-0.7, 0.7) * r)
-            y = f32(kps["y"][t] + rng.uniform(-0.7, 0.7) * r)
+            jit = 0.25 if fuse else 0.7
+            x = f32(kps["x"][t] + rng.uniform(-jit, jit) * r)
+            y = f32(kps["y"][t] + rng.uniform(-jit, jit) * r)
             d = _flip(rng, desc[t], int(rng.randint(0, 75)))
         else:
             t = -1
@@ -86,6 +92,8 @@ def make_case(seed, n=600, nq=700, W=752, H=480, th=1.0, fisheye=False, stereo_g
         if rng.uniform() < 0.03:
             minl, maxl = 0, -1                                  # bCheckLevels == false
         ang = f32(0)
+        if fuse:
+            flags = (flags & ~PQ_BLOCKS) | PQ_BEST_ONLY | PQ_ERROR_GATE
         if last_frame:
             flags |= PQ_BEST_ONLY
             minl, maxl = {"still": (lvl - 1, lvl + 1), "forward": (lvl, -1), "backward": (0, lvl)}[last_frame]
@@ -121,4 +129,5 @@ CASES = {
     "last_still": dict(seed=15, n=800, nq=700, th=7.0, stereo_gate=True, crowd=0.2, last_frame="still"),
     "last_forward": dict(seed=16, n=700, nq=600, th=15.0, crowd=0.4, last_frame="forward"),
     "last_backward_fisheye": dict(seed=17, n=900, nq=800, th=7.0, fisheye=True, crowd=0.3, last_frame="backward"),
+    "fuse": dict(seed=18, n=900, nq=1000, th=3.0, stereo_gate=True, crowd=0.3, fuse=True),
 }

@@ -27,7 +27,7 @@ def _golden_case(g, name):
 def _run(fn, c, **kw):
     return fn(c["kps"], c["desc"], c["queries"], c["qdesc"], c["grid"], n_left=int(c["n_left"][0]), u_right=c.get("u_right"),
               partner=c.get("partner"), taken=c["taken"], th_high=int(c["th_high"][0]), nnratio=float(c["nnratio"][0]),
-              check_orientation=bool(c["check_orientation"][0]), **kw)
+              check_orientation=bool(c["check_orientation"][0]), inv_level_sigma2=c.get("inv_level_sigma2"), **kw)
 
 
 def test_oracle_matches_python_restatement():
@@ -84,7 +84,8 @@ def test_gpu_search_matches_oracle_and_goldens():
                dict(seed=25, n=1, nq=5), dict(seed=26, n=1500, nq=1, th=2.0),
                dict(seed=29, n=2400, nq=3000, th=7.0, stereo_gate=True, crowd=0.3, last_frame="still"),
                dict(seed=30, n=3000, nq=3500, th=15.0, fisheye=True, crowd=0.5, last_frame="forward"),
-               dict(seed=31, n=60, nq=800, th=15.0, crowd=1.0, last_frame="backward")):
+               dict(seed=31, n=60, nq=800, th=15.0, crowd=1.0, last_frame="backward"),
+               dict(seed=32, n=3500, nq=5000, th=3.0, stereo_gate=True, crowd=0.3, fuse=True)):
         c = PC.make_case(**kw)
         want, wtaken, wnm = _run(O.search_by_projection, c)
         out, taken, nm = _run(P.search_by_projection, c)

@@ -385,6 +385,7 @@ def py_search_by_projection(c):
     taken = c["taken"].astype(bool).copy()
     th_high, ratio = int(c["th_high"][0]), f32(c["nnratio"][0])
     check_ori = int(c["check_orientation"][0]) != 0
+    sig = c.get("inv_level_sigma2")
     rot_hist = [[] for _ in range(30)]
     popc = np.array([bin(i).count("1") for i in range(256)], np.int32)
     cells = {}
@@ -434,7 +435,17 @@ def py_search_by_projection(c):
         for i in cand:
             if taken[i]:
                 continue
-            if nleft < 0 and ur is not None and ur[i] > 0 and abs(xr - f32(ur[i])) > r:
+            if (flags & 64) and sig is not None:                 # Fuse: chi-square gate on the reprojection error (ORBmatcher.cc:1714-1740)
+                ex, ey = x - f32(kps["x"][i]), y - f32(kps["y"][i])
+                lim = 5.99
+                e2 = f32(f32(ex * ex) + f32(ey * ey))
+                if ur is not None and ur[i] >= 0:
+                    er = xr - f32(ur[i])
+                    e2 = f32(e2 + f32(er * er))
+                    lim = 7.8
+                if float(f32(e2 * f32(sig[int(kps["octave"][i])]))) > lim:
+                    continue
+            elif nleft < 0 and ur is not None and ur[i] > 0 and abs(xr - f32(ur[i])) > r:
                 continue
             d = int(popc[desc[i] ^ qd[k]].sum())
             if d < best:
