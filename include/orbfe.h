@@ -250,6 +250,28 @@ int orbfe_search_by_bow(int device, const uint8_t* desc_kf, const orbfe_keypoint
                         const int32_t* fv_nodes_f, const int32_t* fv_starts_f, const int32_t* fv_feats_f, int nfv_f, const uint8_t* has_map_point_f,
                         int th_low, float nnratio, int check_orientation, int kf_kf, int32_t* match_f, orbfe_match* kf_out, int* nmatches);
 
+/* Replaces ORBmatcher::SearchForTriangulation(KeyFrame *pKF1, KeyFrame *pKF2, cv::Mat F12, vMatchedPairs, bOnlyStereo, bCoarse)
+ * (src/ORBmatcher.cc:965-1206; LocalMapping::CreateNewMapPoints) for pinhole keyframes without a second camera, for batches of
+ * keyframe pairs in the strided layout of orbfe_search_by_bow_device: features of keyframe 1 without a map point against the features
+ * of keyframe 2 without one, inside the common vocabulary nodes, smallest distance <= th_low (TH_LOW) that keeps away from the epipole
+ * (:1084-1092; d_epipole = ep of pair p, 2 floats; d_scale_factors = mvScaleFactors, 16 floats) and satisfies
+ * Pinhole::epipolarConstrain (src/CameraModels/Pinhole.cpp:135-157) for d_f12 (F12 of pair p, 9 floats row-major; d_level_sigma2 =
+ * pKF2->mvLevelSigma2, 16 floats) or coarse; rotation histogram with check_orientation.  d_u_right (mvuRight, may be NULL) decides
+ * bStereo1/2; d_has_map_point as in orbfe_search_by_bow_device (here a row WITH a map point is left out).
+ * d_match_12[p*row_stride + i] = vMatches12[i]; d_nmatches[p] = the return value. */
+int orbfe_search_for_triangulation_device(int device, int npairs, int max_features, const int32_t* d_pair_1, const int32_t* d_pair_2, const uint8_t* d_desc,
+                                          const orbfe_keypoint* d_kps, const float* d_u_right, int row_stride, const int32_t* d_fv_nodes,
+                                          const int32_t* d_fv_starts, const int32_t* d_fv_feats, const int32_t* d_fv_count, const uint8_t* d_has_map_point,
+                                          const float* d_f12, const float* d_epipole, const float* d_scale_factors, const float* d_level_sigma2, int th_low,
+                                          int only_stereo, int coarse, int check_orientation, int32_t* d_match_12, int32_t* d_nmatches, void* stream);
+/* One pair over host memory (scale_factors / level_sigma2: nlevels entries). */
+int orbfe_search_for_triangulation(int device, const uint8_t* desc_1, const orbfe_keypoint* kps_1, const float* u_right_1, const uint8_t* has_map_point_1, int n_1,
+                                   const int32_t* fv_nodes_1, const int32_t* fv_starts_1, const int32_t* fv_feats_1, int nfv_1, const uint8_t* desc_2,
+                                   const orbfe_keypoint* kps_2, const float* u_right_2, const uint8_t* has_map_point_2, int n_2, const int32_t* fv_nodes_2,
+                                   const int32_t* fv_starts_2, const int32_t* fv_feats_2, int nfv_2, const float* f12, const float* epipole,
+                                   const float* scale_factors, const float* level_sigma2, int nlevels, int th_low, int only_stereo, int coarse,
+                                   int check_orientation, int32_t* match_12, int* nmatches);
+
 /* Replaces the computation of MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:349-423) for many map points at once
  * (SURVEY.md §8f N4): map point p owns the descriptor rows [offsets[p], offsets[p+1]) (the rows of vDescriptors, :352-384);
  * best_idx[p] = BestIdx, the row (relative to offsets[p]) with the least median distance to all rows of the point,

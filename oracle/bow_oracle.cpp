@@ -197,4 +197,93 @@ int orc_search_by_bow(const uint8_t* desc_kf, const orc_keypoint* kps_kf, int n_
     return nmatches;
 }
 
+/* ORBmatcher::SearchForTriangulation(pKF1, pKF2, F12, vMatchedPairs, bOnlyStereo, bCoarse), src/ORBmatcher.cc:965-1206, for pinhole
+ * keyframes without a second camera, with Pinhole::epipolarConstrain (src/CameraModels/Pinhole.cpp:135-157) evaluated on the given
+ * F12 (row-major 3x3).  match_12[i] = vMatches12[i].  Returns nmatches. */
+int orc_search_for_triangulation(const uint8_t* desc_1, const orc_keypoint* kps_1, const float* u_right_1, const uint8_t* has_mp_1, int n_1,
+                                 const int32_t* nodes_1, const int32_t* starts_1, const int32_t* feats_1, int nfv_1, const uint8_t* desc_2,
+                                 const orc_keypoint* kps_2, const float* u_right_2, const uint8_t* has_mp_2, int n_2, const int32_t* nodes_2,
+                                 const int32_t* starts_2, const int32_t* feats_2, int nfv_2, const float* F12, const float* ep,
+                                 const float* scale_factors, const float* level_sigma2, int th_low, int only_stereo, int coarse,
+                                 int check_orientation, int32_t* match_12) {
+    const int HISTO_LENGTH = 30;
+    std::vector<bool> vbMatched2(n_2, false);   /* declared and tested by the reference, never set */
+    for (int i = 0; i < n_1; i++) match_12[i] = -1;
+    int nmatches = 0;
+    std::vector<int> rotHist[HISTO_LENGTH];
+    const float factor = 1.0f / HISTO_LENGTH;
+    int f1it = 0, f2it = 0;
+    while (f1it != nfv_1 && f2it != nfv_2) {
+        if (nodes_1[f1it] == nodes_2[f2it]) {
+            for (int i1 = starts_1[f1it]; i1 < starts_1[f1it + 1]; i1++) {
+                const int idx1 = feats_1[i1];
+                if (has_mp_1 && has_mp_1[idx1]) continue;
+                const bool bStereo1 = u_right_1 && u_right_1[idx1] >= 0;
+                if (only_stereo && !bStereo1) continue;
+                const orc_keypoint& kp1 = kps_1[idx1];
+                const uint8_t* d1 = desc_1 + (size_t)idx1 * 32;
+                int bestDist = th_low, bestIdx2 = -1;
+                for (int i2 = starts_2[f2it]; i2 < starts_2[f2it + 1]; i2++) {
+                    const int idx2 = feats_2[i2];
+                    if (vbMatched2[idx2] || (has_mp_2 && has_mp_2[idx2])) continue;
+                    const bool bStereo2 = u_right_2 && u_right_2[idx2] >= 0;
+                    if (only_stereo && !bStereo2) continue;
+                    const int dist = orc_descriptor_distance(d1, desc_2 + (size_t)idx2 * 32);
+                    if (dist > th_low || dist > bestDist) continue;
+                    const orc_keypoint& kp2 = kps_2[idx2];
+                    if (!bStereo1 && !bStereo2) {
+                        const float distex = ep[0] - kp2.x, distey = ep[1] - kp2.y;
+                        if (distex * distex + distey * distey < 100 * scale_factors[kp2.octave]) continue;
+                    }
+                    bool ok = coarse != 0;
+                    if (!ok) {   /* Pinhole::epipolarConstrain */
+                        const float a = kp1.x * F12[0] + kp1.y * F12[3] + F12[6];
+                        const float b = kp1.x * F12[1] + kp1.y * F12[4] + F12[7];
+                        const float c = kp1.x * F12[2] + kp1.y * F12[5] + F12[8];
+                        const float num = a * kp2.x + b * kp2.y + c;
+                        const float den = a * a + b * b;
+                        if (den != 0) {
+                            const float dsqr = num * num / den;
+                            ok = dsqr < 3.84 * level_sigma2[kp2.octave];
+                        }
+                    }
+                    if (ok) { bestIdx2 = idx2; bestDist = dist; }
+                }
+                if (bestIdx2 >= 0) {
+                    match_12[idx1] = bestIdx2;
+                    nmatches++;
+                    if (check_orientation) {
+                        float rot = kp1.angle - kps_2[bestIdx2].angle;
+                        if (rot < 0.0) rot += 360.0f;
+                        int bin = (int)std::round(rot * factor);
+                        if (bin == HISTO_LENGTH) bin = 0;
+                        if (bin >= 0 && bin < HISTO_LENGTH) rotHist[bin].push_back(idx1);
+                    }
+                }
+            }
+            f1it++; f2it++;
+        } else if (nodes_1[f1it] < nodes_2[f2it]) {
+            while (f1it != nfv_1 && nodes_1[f1it] < nodes_2[f2it]) f1it++;
+        } else {
+            while (f2it != nfv_2 && nodes_2[f2it] < nodes_1[f1it]) f2it++;
+        }
+    }
+    if (check_orientation) {
+        int ind1 = -1, ind2 = -1, ind3 = -1, max1 = 0, max2 = 0, max3 = 0;
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            const int c = (int)rotHist[i].size();
+            if (c > max1) { max3 = max2; max2 = max1; max1 = c; ind3 = ind2; ind2 = ind1; ind1 = i; }
+            else if (c > max2) { max3 = max2; max2 = c; ind3 = ind2; ind2 = i; }
+            else if (c > max3) { max3 = c; ind3 = i; }
+        }
+        if (max2 < 0.1f * (float)max1) { ind2 = -1; ind3 = -1; }
+        else if (max3 < 0.1f * (float)max1) { ind3 = -1; }
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            if (i == ind1 || i == ind2 || i == ind3) continue;
+            for (int idx1 : rotHist[i]) { match_12[idx1] = -1; nmatches--; }
+        }
+    }
+    return nmatches;
+}
+
 }  /* extern "C" */

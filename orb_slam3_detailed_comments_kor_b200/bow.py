@@ -97,3 +97,23 @@ def search_by_bow(desc_kf, kps_kf, fv_kf, has_map_point, desc_f, kps_f, fv_f, th
                                          ptr(mpf) if mpf is not None else None, th_low, C.c_float(nnratio), int(check_orientation), int(kf_kf),
                                          ptr(match_f), ptr(kf_out), C.byref(nm)))
     return match_f[:desc_f.shape[0]], kf_out[:desc_kf.shape[0]], nm.value
+
+
+def search_for_triangulation(desc_1, kps_1, u_right_1, has_mp_1, fv_1, desc_2, kps_2, u_right_2, has_mp_2, fv_2, f12, epipole, scale_factors,
+                             level_sigma2, th_low=50, only_stereo=False, coarse=False, check_orientation=True, device=0):
+    """ORBmatcher::SearchForTriangulation(pKF1, pKF2, F12, ..., bOnlyStereo, bCoarse) (src/ORBmatcher.cc:965-1206) for one pinhole
+    keyframe pair on the host.  Returns (vMatches12[n1], nmatches)."""
+    c = lambda a, t: None if a is None else np.ascontiguousarray(a, t)  # noqa: E731
+    d1, d2, k1, k2 = c(desc_1, np.uint8), c(desc_2, np.uint8), c(kps_1, KP_DTYPE), c(kps_2, KP_DTYPE)
+    u1, u2, m1, m2 = c(u_right_1, np.float32), c(u_right_2, np.float32), c(has_mp_1, np.uint8), c(has_mp_2, np.uint8)
+    n1, s1, f1 = _fv_arrays(fv_1)
+    n2, s2, f2 = _fv_arrays(fv_2)
+    F, ep = c(np.asarray(f12).reshape(9), np.float32), c(epipole, np.float32)
+    sf, ls = c(scale_factors, np.float32), c(level_sigma2, np.float32)
+    out = np.zeros(max(d1.shape[0], 1), np.int32)
+    nm = C.c_int(0)
+    p = lambda a: ptr(a) if a is not None else None  # noqa: E731
+    check(_lib.lib().orbfe_search_for_triangulation(device, p(d1), p(k1), p(u1), p(m1), d1.shape[0], p(n1), p(s1), p(f1), len(n1), p(d2), p(k2), p(u2), p(m2),
+                                                    d2.shape[0], p(n2), p(s2), p(f2), len(n2), p(F), p(ep), p(sf), p(ls), len(sf), th_low, int(only_stereo),
+                                                    int(coarse), int(check_orientation), p(out), C.byref(nm)))
+    return out[:d1.shape[0]], nm.value

@@ -347,6 +347,131 @@ __global__ void __launch_bounds__(SB_NT) k_search_by_bow(int maxF, const int* __
     if (tid == 0 && nmatches) nmatches[pr] = s_total;
 }
 
+/* ---------------------------------------------------------------------------------------- SearchForTriangulation */
+/* ORBmatcher::SearchForTriangulation(KeyFrame *pKF1, KeyFrame *pKF2, cv::Mat F12, vMatchedPairs, bOnlyStereo, bCoarse)
+ * (/root/reference/src/ORBmatcher.cc:965-1206), pinhole rigs (no mpCamera2): for every vocabulary node present in both feature
+ * vectors, every feature of keyframe 1 WITHOUT a map point looks, among the features of keyframe 2 in that node that have no map
+ * point either, for the smallest descriptor distance <= TH_LOW whose keypoint is not too close to the epipole (both monocular:
+ * |ep - kp2|^2 >= 100 * mvScaleFactors[octave2]) and lies on the epipolar line of kp1 (Pinhole::epipolarConstrain,
+ * src/CameraModels/Pinhole.cpp:135-157: dsqr < 3.84 * mvLevelSigma2[octave2]) or bCoarse; `dist > bestDist` skips, so among equal
+ * distances the LAST candidate wins.  This version of the reference never sets vbMatched2, so the features of keyframe 1 are
+ * independent of each other: one thread = one feature, no rounds.  Then the rotation histogram as in SearchByBoW. */
+__global__ void __launch_bounds__(SB_NT) k_search_for_triangulation(int maxF, const int* __restrict__ pair1, const int* __restrict__ pair2,
+                                                                    const uint4* __restrict__ desc, const orbfe_keypoint* __restrict__ kps,
+                                                                    const float* __restrict__ uRight, int rowStride, const int* __restrict__ fvNodes,
+                                                                    const int* __restrict__ fvStarts, const int* __restrict__ fvFeats,
+                                                                    const int* __restrict__ fvCount, const uint8_t* __restrict__ hasMp,
+                                                                    const float* __restrict__ f12All, const float* __restrict__ epAll,
+                                                                    const float* __restrict__ scaleFactors, const float* __restrict__ levelSigma2, int thLow,
+                                                                    int onlyStereo, int coarse, int checkOri, int* __restrict__ match12,
+                                                                    int* __restrict__ nmatches) {
+    __shared__ int s_rot[32];
+    __shared__ int s_total;
+    const int tid = threadIdx.x, pr = blockIdx.x;
+    const int a = pair1[pr], b = pair2[pr];
+    const int* nodesA = fvNodes + (size_t)a * maxF; const int* startsA = fvStarts + (size_t)a * (maxF + 1); const int* featsA = fvFeats + (size_t)a * maxF;
+    const int* nodesB = fvNodes + (size_t)b * maxF; const int* startsB = fvStarts + (size_t)b * (maxF + 1); const int* featsB = fvFeats + (size_t)b * maxF;
+    const int nnA = fvCount[a], nnB = fvCount[b];
+    const uint4* descA = desc + (size_t)a * rowStride * 2; const uint4* descB = desc + (size_t)b * rowStride * 2;
+    const orbfe_keypoint* kA = kps + (size_t)a * rowStride; const orbfe_keypoint* kB = kps + (size_t)b * rowStride;
+    const float* urA = uRight ? uRight + (size_t)a * rowStride : nullptr; const float* urB = uRight ? uRight + (size_t)b * rowStride : nullptr;
+    const uint8_t* mpA = hasMp ? hasMp + (size_t)a * rowStride : nullptr; const uint8_t* mpB = hasMp ? hasMp + (size_t)b * rowStride : nullptr;
+    const float* F = f12All + (size_t)pr * 9;
+    const float epx = epAll[2 * pr], epy = epAll[2 * pr + 1];
+    int* m12 = match12 + (size_t)pr * rowStride;
+    for (int i = tid; i < rowStride; i += SB_NT) m12[i] = -1;
+    if (tid < 32) s_rot[tid] = 0;
+    if (tid == 0) s_total = 0;
+    __syncthreads();
+    /* one warp walks the nodes of keyframe 1 in turn (binary search for the node in keyframe 2), its lanes take the node's features */
+    for (int e = tid >> 5; e < nnA; e += SB_NT / 32) {
+        const int node = nodesA[e];
+        int lo = 0, hi = nnB;
+        while (lo < hi) { const int mid = (lo + hi) >> 1; if (nodesB[mid] < node) lo = mid + 1; else hi = mid; }
+        if (lo >= nnB || nodesB[lo] != node) continue;
+        const int fb0 = startsB[lo], fb1 = startsB[lo + 1];
+        for (int j = startsA[e] + (tid & 31); j < startsA[e + 1]; j += 32) {
+            const int idx1 = featsA[j];
+            if (mpA && mpA[idx1]) continue;                                   /* if(pMP1) continue; */
+            const bool stereo1 = urA && __ldg(urA + idx1) >= 0;
+            if (onlyStereo && !stereo1) continue;
+            const float x1 = __ldg(&kA[idx1].x), y1 = __ldg(&kA[idx1].y);
+            /* epipolar line of kp1 in image 2: l = x1' F12 */
+            const float la = __fadd_rn(__fadd_rn(__fmul_rn(x1, F[0]), __fmul_rn(y1, F[3])), F[6]);
+            const float lb = __fadd_rn(__fadd_rn(__fmul_rn(x1, F[1]), __fmul_rn(y1, F[4])), F[7]);
+            const float lc = __fadd_rn(__fadd_rn(__fmul_rn(x1, F[2]), __fmul_rn(y1, F[5])), F[8]);
+            const float den = __fadd_rn(__fmul_rn(la, la), __fmul_rn(lb, lb));
+            const uint4 qa = __ldg(descA + 2 * idx1), qb = __ldg(descA + 2 * idx1 + 1);
+            int bestDist = thLow, bestIdx2 = -1;
+            for (int c = fb0; c < fb1; c++) {
+                const int idx2 = featsB[c];
+                if (mpB && mpB[idx2]) continue;                               /* if(vbMatched2[idx2] || pMP2) continue; (vbMatched2 is never set) */
+                const bool stereo2 = urB && __ldg(urB + idx2) >= 0;
+                if (onlyStereo && !stereo2) continue;
+                const int dist = bow_ham(qa, qb, __ldg(descB + 2 * idx2), __ldg(descB + 2 * idx2 + 1));
+                if (dist > thLow || dist > bestDist) continue;
+                const float x2 = __ldg(&kB[idx2].x), y2 = __ldg(&kB[idx2].y);
+                const int oct2 = __ldg(&kB[idx2].octave);
+                if (!stereo1 && !stereo2) {
+                    const float dex = __fsub_rn(epx, x2), dey = __fsub_rn(epy, y2);
+                    if (__fadd_rn(__fmul_rn(dex, dex), __fmul_rn(dey, dey)) < __fmul_rn(100.0f, __ldg(scaleFactors + oct2))) continue;
+                }
+                bool ok = coarse != 0;
+                if (!ok && den != 0.0f) {
+                    const float num = __fadd_rn(__fadd_rn(__fmul_rn(la, x2), __fmul_rn(lb, y2)), lc);
+                    const float dsqr = __fdiv_rn(__fmul_rn(num, num), den);
+                    ok = (double)dsqr < 3.84 * (double)__ldg(levelSigma2 + oct2);
+                }
+                if (ok) { bestIdx2 = idx2; bestDist = dist; }
+            }
+            if (bestIdx2 >= 0) {
+                m12[idx1] = bestIdx2;
+                if (checkOri) {
+                    float rot = __ldg(&kA[idx1].angle) - __ldg(&kB[bestIdx2].angle);
+                    if (rot < 0.0f) rot += 360.0f;
+                    int bin = (int)roundf(rot * (1.0f / 30.0f));
+                    if (bin == 30) bin = 0;
+                    if (bin >= 0 && bin < 30) atomicAdd(&s_rot[bin], 1);
+                }
+            }
+        }
+    }
+    __syncthreads();
+    if (checkOri) {
+        if (tid == 0) {
+            int ind1 = -1, ind2 = -1, ind3 = -1, max1 = 0, max2 = 0, max3 = 0;
+            for (int i = 0; i < 30; i++) {
+                const int c = s_rot[i];
+                if (c > max1) { max3 = max2; max2 = max1; max1 = c; ind3 = ind2; ind2 = ind1; ind1 = i; }
+                else if (c > max2) { max3 = max2; max2 = c; ind3 = ind2; ind2 = i; }
+                else if (c > max3) { max3 = c; ind3 = i; }
+            }
+            if ((float)max2 < 0.1f * (float)max1) { ind2 = -1; ind3 = -1; }
+            else if ((float)max3 < 0.1f * (float)max1) { ind3 = -1; }
+            s_rot[30] = ind1; s_rot[31] = (ind2 & 0xFF) | ((ind3 & 0xFF) << 8);
+        }
+        __syncthreads();
+        const int ind1 = s_rot[30], ind2 = (int)(signed char)(s_rot[31] & 0xFF), ind3 = (int)(signed char)((s_rot[31] >> 8) & 0xFF);
+        for (int i = tid; i < rowStride; i += SB_NT) {
+            const int r2 = m12[i];
+            if (r2 < 0) continue;
+            float rot = __ldg(&kA[i].angle) - __ldg(&kB[r2].angle);
+            if (rot < 0.0f) rot += 360.0f;
+            int bin = (int)roundf(rot * (1.0f / 30.0f));
+            if (bin == 30) bin = 0;
+            if (bin >= 0 && bin < 30 && bin != ind1 && bin != ind2 && bin != ind3) m12[i] = -1;
+        }
+        __syncthreads();
+    }
+    int cnt = 0;
+    for (int i = tid; i < rowStride; i += SB_NT) cnt += m12[i] >= 0 ? 1 : 0;
+#pragma unroll
+    for (int o = 16; o; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+    if ((tid & 31) == 0) atomicAdd(&s_total, cnt);
+    __syncthreads();
+    if (tid == 0 && nmatches) nmatches[pr] = s_total;
+}
+
 static int bow_norm_of(int scoring) { return scoring == 5 ? 0 : (scoring == 1 ? 2 : 1); }   /* ScoringObject.h:73-90 */
 
 extern "C" {
@@ -571,6 +696,88 @@ int orbfe_search_by_bow(int device, const uint8_t* desc_kf, const orbfe_keypoint
     cudaFree(d);
     if (rc != ORBFE_OK) return rc;
     if (e != cudaSuccess) return orbfe_cuda_fail(e, "search_by_bow");
+    return ORBFE_OK;
+}
+
+int orbfe_search_for_triangulation_device(int device, int npairs, int max_features, const int32_t* d_pair_1, const int32_t* d_pair_2, const uint8_t* d_desc,
+                                          const orbfe_keypoint* d_kps, const float* d_u_right, int row_stride, const int32_t* d_fv_nodes,
+                                          const int32_t* d_fv_starts, const int32_t* d_fv_feats, const int32_t* d_fv_count, const uint8_t* d_has_map_point,
+                                          const float* d_f12, const float* d_epipole, const float* d_scale_factors, const float* d_level_sigma2, int th_low,
+                                          int only_stereo, int coarse, int check_orientation, int32_t* d_match_12, int32_t* d_nmatches, void* stream) {
+    if (npairs < 1 || !d_pair_1 || !d_pair_2 || !d_desc || !d_kps || !d_fv_nodes || !d_fv_starts || !d_fv_feats || !d_fv_count || !d_f12 || !d_epipole ||
+        !d_scale_factors || !d_level_sigma2 || !d_match_12 || row_stride < 1) { orbfe_set_error("bad argument"); return ORBFE_E_INVALID; }
+    if (max_features < 1 || max_features > BOW_MAXF || row_stride > BOW_MAXF) { orbfe_set_error("at most %d features per frame", BOW_MAXF); return ORBFE_E_CAPACITY; }
+    if ((uintptr_t)d_desc & 15) { orbfe_set_error("descriptor array must be 16-byte aligned"); return ORBFE_E_INVALID; }
+    ORBFE_CUDA(cudaSetDevice(device));
+    k_search_for_triangulation<<<npairs, SB_NT, 0, (cudaStream_t)stream>>>(max_features, d_pair_1, d_pair_2, (const uint4*)d_desc, d_kps, d_u_right, row_stride,
+                                                                           d_fv_nodes, d_fv_starts, d_fv_feats, d_fv_count, d_has_map_point, d_f12, d_epipole,
+                                                                           d_scale_factors, d_level_sigma2, th_low, only_stereo ? 1 : 0, coarse ? 1 : 0,
+                                                                           check_orientation ? 1 : 0, d_match_12, d_nmatches);
+    ORBFE_CUDA(cudaGetLastError());
+    return ORBFE_OK;
+}
+
+int orbfe_search_for_triangulation(int device, const uint8_t* desc_1, const orbfe_keypoint* kps_1, const float* u_right_1, const uint8_t* has_map_point_1, int n_1,
+                                   const int32_t* fv_nodes_1, const int32_t* fv_starts_1, const int32_t* fv_feats_1, int nfv_1, const uint8_t* desc_2,
+                                   const orbfe_keypoint* kps_2, const float* u_right_2, const uint8_t* has_map_point_2, int n_2, const int32_t* fv_nodes_2,
+                                   const int32_t* fv_starts_2, const int32_t* fv_feats_2, int nfv_2, const float* f12, const float* epipole,
+                                   const float* scale_factors, const float* level_sigma2, int nlevels, int th_low, int only_stereo, int coarse,
+                                   int check_orientation, int32_t* match_12, int* nmatches) {
+    if (n_1 < 0 || n_2 < 0 || nfv_1 < 0 || nfv_2 < 0 || !match_12 || !f12 || !epipole || !scale_factors || !level_sigma2 || nlevels < 1 || nlevels > 16 ||
+        (n_1 && (!desc_1 || !kps_1)) || (n_2 && (!desc_2 || !kps_2)) || (nfv_1 && (!fv_nodes_1 || !fv_starts_1 || !fv_feats_1)) ||
+        (nfv_2 && (!fv_nodes_2 || !fv_starts_2 || !fv_feats_2))) { orbfe_set_error("bad argument"); return ORBFE_E_INVALID; }
+    const int S = std::max(std::max(n_1, n_2), 1);
+    if (S > BOW_MAXF) { orbfe_set_error("at most %d features per frame", BOW_MAXF); return ORBFE_E_CAPACITY; }
+    if (nfv_1 > S || nfv_2 > S || (nfv_1 && fv_starts_1[nfv_1] > S) || (nfv_2 && fv_starts_2[nfv_2] > S)) { orbfe_set_error("feature vector longer than the frame"); return ORBFE_E_INVALID; }
+    if (nmatches) *nmatches = 0;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev) {
+        orbfe_set_error("no usable CUDA device %d (found %d); this library has no CPU path", device, ndev);
+        return ORBFE_E_CUDA;
+    }
+    ORBFE_CUDA(cudaSetDevice(device));
+    std::vector<uint8_t> hDesc((size_t)2 * S * 32, 0), hMp((size_t)2 * S, 0);
+    std::vector<orbfe_keypoint> hKps((size_t)2 * S);
+    std::vector<float> hUr((size_t)2 * S, -1.0f), hPar(9 + 2 + 16 + 16, 0.0f);
+    std::vector<int32_t> hNodes((size_t)2 * S, 0), hStarts((size_t)2 * (S + 1), 0), hFeats((size_t)2 * S, 0), hMisc(4);
+    memset(hKps.data(), 0, hKps.size() * sizeof(orbfe_keypoint));
+    if (n_1) { memcpy(hDesc.data(), desc_1, (size_t)n_1 * 32); memcpy(hKps.data(), kps_1, (size_t)n_1 * sizeof(orbfe_keypoint)); }
+    if (n_2) { memcpy(hDesc.data() + (size_t)S * 32, desc_2, (size_t)n_2 * 32); memcpy(hKps.data() + S, kps_2, (size_t)n_2 * sizeof(orbfe_keypoint)); }
+    if (u_right_1 && n_1) memcpy(hUr.data(), u_right_1, (size_t)n_1 * 4);
+    if (u_right_2 && n_2) memcpy(hUr.data() + S, u_right_2, (size_t)n_2 * 4);
+    if (has_map_point_1 && n_1) memcpy(hMp.data(), has_map_point_1, (size_t)n_1);
+    if (has_map_point_2 && n_2) memcpy(hMp.data() + S, has_map_point_2, (size_t)n_2);
+    if (nfv_1) { memcpy(hNodes.data(), fv_nodes_1, (size_t)nfv_1 * 4); memcpy(hStarts.data(), fv_starts_1, (size_t)(nfv_1 + 1) * 4); memcpy(hFeats.data(), fv_feats_1, (size_t)fv_starts_1[nfv_1] * 4); }
+    if (nfv_2) { memcpy(hNodes.data() + S, fv_nodes_2, (size_t)nfv_2 * 4); memcpy(hStarts.data() + S + 1, fv_starts_2, (size_t)(nfv_2 + 1) * 4); memcpy(hFeats.data() + S, fv_feats_2, (size_t)fv_starts_2[nfv_2] * 4); }
+    memcpy(hPar.data(), f12, 9 * 4); memcpy(hPar.data() + 9, epipole, 2 * 4);
+    memcpy(hPar.data() + 11, scale_factors, (size_t)nlevels * 4); memcpy(hPar.data() + 27, level_sigma2, (size_t)nlevels * 4);
+    hMisc[0] = nfv_1; hMisc[1] = nfv_2; hMisc[2] = 0; hMisc[3] = 1;
+    size_t off = 0;
+    auto take = [&](size_t bytes) { const size_t o = off; off += (bytes + 255) & ~(size_t)255; return o; };
+    const size_t oDesc = take(hDesc.size()), oKps = take(hKps.size() * sizeof(orbfe_keypoint)), oUr = take(hUr.size() * 4), oMp = take(hMp.size());
+    const size_t oNodes = take(hNodes.size() * 4), oStarts = take(hStarts.size() * 4), oFeats = take(hFeats.size() * 4), oPar = take(hPar.size() * 4);
+    const size_t oMisc = take(16), oMatch = take((size_t)S * 4), oNm = take(4);
+    uint8_t* d = nullptr;
+    ORBFE_CUDA(cudaMalloc((void**)&d, off));
+    cudaError_t e = cudaMemcpy(d + oDesc, hDesc.data(), hDesc.size(), cudaMemcpyHostToDevice);
+#define ST_UP(o, v, bytes) if (e == cudaSuccess) e = cudaMemcpy(d + (o), (v), (bytes), cudaMemcpyHostToDevice)
+    ST_UP(oKps, hKps.data(), hKps.size() * sizeof(orbfe_keypoint)); ST_UP(oUr, hUr.data(), hUr.size() * 4); ST_UP(oMp, hMp.data(), hMp.size());
+    ST_UP(oNodes, hNodes.data(), hNodes.size() * 4); ST_UP(oStarts, hStarts.data(), hStarts.size() * 4); ST_UP(oFeats, hFeats.data(), hFeats.size() * 4);
+    ST_UP(oPar, hPar.data(), hPar.size() * 4); ST_UP(oMisc, hMisc.data(), 16);
+#undef ST_UP
+    int rc = ORBFE_OK;
+    const float* dp = (const float*)(d + oPar);
+    if (e == cudaSuccess)
+        rc = orbfe_search_for_triangulation_device(device, 1, S, (const int32_t*)(d + oMisc) + 2, (const int32_t*)(d + oMisc) + 3, d + oDesc, (const orbfe_keypoint*)(d + oKps),
+                                                   (const float*)(d + oUr), S, (const int32_t*)(d + oNodes), (const int32_t*)(d + oStarts), (const int32_t*)(d + oFeats),
+                                                   (const int32_t*)(d + oMisc), d + oMp, dp, dp + 9, dp + 11, dp + 27, th_low, only_stereo, coarse, check_orientation,
+                                                   (int32_t*)(d + oMatch), (int32_t*)(d + oNm), nullptr);
+    if (rc == ORBFE_OK && e == cudaSuccess) e = cudaDeviceSynchronize();
+    if (rc == ORBFE_OK && e == cudaSuccess && n_1) e = cudaMemcpy(match_12, d + oMatch, (size_t)n_1 * 4, cudaMemcpyDeviceToHost);
+    if (rc == ORBFE_OK && e == cudaSuccess && nmatches) e = cudaMemcpy(nmatches, d + oNm, 4, cudaMemcpyDeviceToHost);
+    cudaFree(d);
+    if (rc != ORBFE_OK) return rc;
+    if (e != cudaSuccess) return orbfe_cuda_fail(e, "search_for_triangulation");
     return ORBFE_OK;
 }
 

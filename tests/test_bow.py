@@ -324,3 +324,153 @@ def test_gpu_extract_bow_search_chain_on_device():
         assert (match[p, cnt[b]:] == -1).all()
     assert nm[:3].sum() > 0                              # (a random vocabulary separates real descriptors poorly: few, but some, matches)
     voc.close(); ex.close()
+
+
+# ------------------------------------------------------------------------------------------- SearchForTriangulation
+def make_triangulation_pair(seed, rows, n):
+    """Two pinhole keyframes one baseline apart: keyframe 2 sees keyframe 1's features shifted along x (the epipolar lines are
+    the image rows), with some vertical noise so that the epipolar test cuts both ways."""
+    from oracle.orb_oracle import KP_DTYPE
+    rng = np.random.RandomState(seed)
+    f32 = np.float32
+    d1 = make_features(seed, rows[2], n)
+    k1 = np.zeros(n, KP_DTYPE)
+    k1["x"], k1["y"] = rng.uniform(20, 730, n), rng.uniform(20, 460, n)
+    k1["octave"] = np.minimum(rng.geometric(0.35, n) - 1, 7)
+    k1["angle"] = rng.uniform(0, 360, n)
+    perm = rng.permutation(n)
+    d2, k2 = d1[perm].copy(), k1[perm].copy()
+    for i in range(n):
+        nb = int(rng.randint(0, 30)) if rng.uniform() < 0.8 else 110
+        for b in rng.choice(256, size=nb, replace=False):
+            d2[i, b >> 3] ^= np.uint8(1 << (b & 7))
+    k2["x"] = (k2["x"] - rng.uniform(2, 60, n)).astype(f32)
+    k2["y"] = (k2["y"] + np.where(rng.uniform(size=n) < 0.7, rng.uniform(-1.5, 1.5, n), rng.uniform(-12, 12, n))).astype(f32)
+    k2["angle"] = (k2["angle"] - 10 + np.where(rng.uniform(size=n) < 0.85, rng.uniform(-4, 4, n), rng.uniform(0, 360, n))) % 360
+    u1 = np.where(rng.uniform(size=n) < 0.5, k1["x"] - 5, -1).astype(f32)
+    u2 = np.where(rng.uniform(size=n) < 0.5, k2["x"] - 5, -1).astype(f32)
+    mp1, mp2 = (rng.uniform(size=n) < 0.3).astype(np.uint8), (rng.uniform(size=n) < 0.3).astype(np.uint8)
+    K = np.array([[458.654, 0, 367.215], [0, 457.296, 248.375], [0, 0, 1]], np.float64)
+    tx = np.array([[0, 0, 0], [0, 0, -0.11], [0, 0.11, 0]], np.float64)          # [t12]x for t12 = (0.11, 0, 0), R12 = I
+    F = (np.linalg.inv(K).T @ tx @ np.linalg.inv(K)).astype(f32)
+    ep = np.array([300.0, 240.0], f32)                                            # any point: the rule only needs to be applied identically
+    scale = np.array([f32(1.2) ** i for i in range(8)], f32)
+    sigma2 = (scale * scale).astype(f32)
+    return d1, k1, u1, mp1, d2, k2, u2, mp2, F, ep, scale, sigma2
+
+
+def python_search_for_triangulation(d1, k1, u1, mp1, fv1, d2, k2, u2, mp2, fv2, F, ep, scale, sigma2, th_low, only_stereo, coarse, check_ori):
+    """ORBmatcher::SearchForTriangulation + Pinhole::epipolarConstrain in plain Python (written from the reference sources)."""
+    f32 = np.float32
+    F = np.asarray(F, f32).reshape(3, 3)
+    m12 = np.full(len(d1), -1, np.int32)
+    hist = [[] for _ in range(30)]
+    nm = 0
+    for node in sorted(set(fv1) & set(fv2)):
+        for i1 in fv1[node]:
+            if mp1[i1]:
+                continue
+            st1 = u1[i1] >= 0
+            if only_stereo and not st1:
+                continue
+            x1, y1 = f32(k1["x"][i1]), f32(k1["y"][i1])
+            best, bi = th_low, -1
+            for i2 in fv2[node]:
+                if mp2[i2]:
+                    continue
+                st2 = u2[i2] >= 0
+                if only_stereo and not st2:
+                    continue
+                d = int(POPC[d1[i1] ^ d2[i2]].sum())
+                if d > th_low or d > best:
+                    continue
+                x2, y2, o2 = f32(k2["x"][i2]), f32(k2["y"][i2]), int(k2["octave"][i2])
+                if not st1 and not st2:
+                    ex, ey = f32(ep[0] - x2), f32(ep[1] - y2)
+                    if f32(f32(ex * ex) + f32(ey * ey)) < f32(f32(100) * scale[o2]):
+                        continue
+                ok = coarse
+                if not ok:
+                    a = f32(f32(f32(x1 * F[0, 0]) + f32(y1 * F[1, 0])) + F[2, 0])
+                    b = f32(f32(f32(x1 * F[0, 1]) + f32(y1 * F[1, 1])) + F[2, 1])
+                    c = f32(f32(f32(x1 * F[0, 2]) + f32(y1 * F[1, 2])) + F[2, 2])
+                    num = f32(f32(f32(a * x2) + f32(b * y2)) + c)
+                    den = f32(f32(a * a) + f32(b * b))
+                    if den != 0:
+                        ok = float(f32(f32(num * num) / den)) < 3.84 * float(sigma2[o2])
+                if ok:
+                    best, bi = d, i2
+            if bi >= 0:
+                m12[i1] = bi
+                nm += 1
+                if check_ori:
+                    rot = f32(k1["angle"][i1]) - f32(k2["angle"][bi])
+                    if rot < 0:
+                        rot = f32(rot + f32(360))
+                    b = int(np.floor(abs(float(f32(rot * f32(f32(1) / f32(30))))) + 0.5))
+                    hist[0 if b == 30 else b].append(i1)
+    if check_ori:
+        ind, mx = [-1, -1, -1], [0, 0, 0]
+        for i, h in enumerate(hist):
+            sz = len(h)
+            if sz > mx[0]:
+                mx = [sz, mx[0], mx[1]]; ind = [i, ind[0], ind[1]]
+            elif sz > mx[1]:
+                mx = [mx[0], sz, mx[1]]; ind = [ind[0], i, ind[1]]
+            elif sz > mx[2]:
+                mx[2] = sz; ind[2] = i
+        if f32(mx[1]) < f32(0.1) * f32(mx[0]):
+            ind[1] = ind[2] = -1
+        elif f32(mx[2]) < f32(0.1) * f32(mx[0]):
+            ind[2] = -1
+        for i in range(30):
+            if i not in ind:
+                for i1 in hist[i]:
+                    m12[i1] = -1
+                    nm -= 1
+    return m12, nm
+
+
+ST_CONFIGS = [(4, 3, 1, 41, 700), (10, 3, 2, 42, 1200), (3, 3, 2, 43, 500)]   # k, L, levelsup, seed, n
+
+
+def _triangulation_inputs(k, L, levelsup, seed, n):
+    rows = make_vocabulary(seed, k, L)
+    voc = O.OracleVocabulary(k, L, 0, 0, *rows)
+    t = make_triangulation_pair(seed, rows, n)
+    fv1, fv2 = voc.transform(t[0], levelsup)["feat_vec"], voc.transform(t[4], levelsup)["feat_vec"]
+    return t, fv1, fv2
+
+
+def test_oracle_search_for_triangulation_matches_python():
+    for cfg in ST_CONFIGS:
+        (d1, k1, u1, mp1, d2, k2, u2, mp2, F, ep, scale, sigma2), fv1, fv2 = _triangulation_inputs(*cfg)
+        seen = 0
+        for only_stereo, coarse, ori in ((False, False, True), (True, False, True), (False, True, False), (False, False, False)):
+            got, nm = O.search_for_triangulation(d1, k1, u1, mp1, fv1, d2, k2, u2, mp2, fv2, F, ep, scale, sigma2, 50, only_stereo, coarse, ori)
+            want, wnm = python_search_for_triangulation(d1, k1, u1, mp1, fv1, d2, k2, u2, mp2, fv2, F, ep, scale, sigma2, 50, only_stereo, coarse, ori)
+            assert np.array_equal(got, want) and nm == wnm, (cfg, only_stereo, coarse, ori)
+            seen += nm
+        assert seen > 100
+        # the epipolar test must cut: coarse accepts more than the strict run
+        strict = O.search_for_triangulation(d1, k1, u1, mp1, fv1, d2, k2, u2, mp2, fv2, F, ep, scale, sigma2, 50, False, False, False)[1]
+        loose = O.search_for_triangulation(d1, k1, u1, mp1, fv1, d2, k2, u2, mp2, fv2, F, ep, scale, sigma2, 50, False, True, False)[1]
+        assert loose > strict > 0
+
+
+@pytest.mark.gpu
+def test_gpu_search_for_triangulation_matches_oracle():
+    from orb_slam3_detailed_comments_kor_b200 import bow as B
+    for cfg in ST_CONFIGS + [(2, 2, 1, 44, 3000), (10, 4, 2, 45, 4096)]:
+        (d1, k1, u1, mp1, d2, k2, u2, mp2, F, ep, scale, sigma2), fv1, fv2 = _triangulation_inputs(*cfg)
+        for only_stereo, coarse, ori in ((False, False, True), (True, False, True), (False, True, False), (False, False, False)):
+            want = O.search_for_triangulation(d1, k1, u1, mp1, fv1, d2, k2, u2, mp2, fv2, F, ep, scale, sigma2, 50, only_stereo, coarse, ori)
+            got = B.search_for_triangulation(d1, k1, u1, mp1, fv1, d2, k2, u2, mp2, fv2, F, ep, scale, sigma2, 50, only_stereo, coarse, ori)
+            assert np.array_equal(got[0], want[0]) and got[1] == want[1], (cfg, only_stereo, coarse, ori)
+    # monocular keyframes (no mvuRight at all), empty sides
+    (d1, k1, u1, mp1, d2, k2, u2, mp2, F, ep, scale, sigma2), fv1, fv2 = _triangulation_inputs(4, 3, 1, 46, 300)
+    want = O.search_for_triangulation(d1, k1, None, mp1, fv1, d2, k2, None, mp2, fv2, F, ep, scale, sigma2)
+    got = B.search_for_triangulation(d1, k1, None, mp1, fv1, d2, k2, None, mp2, fv2, F, ep, scale, sigma2)
+    assert np.array_equal(got[0], want[0]) and got[1] == want[1]
+    got = B.search_for_triangulation(d1[:0], k1[:0], None, None, {}, d2, k2, None, mp2, fv2, F, ep, scale, sigma2)
+    assert got[0].shape == (0,) and got[1] == 0
