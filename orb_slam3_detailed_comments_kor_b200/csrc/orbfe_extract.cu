@@ -72,8 +72,8 @@ static __device__ __forceinline__ uint32_t resize_vblend(uint32_t h0, uint32_t h
 
 __global__ void __launch_bounds__(256) k_pyramid_level(const __grid_constant__ ExDesc d, ExBuffers b, const __grid_constant__ ResizeArgs a) {
     /* block = 32 x 8: a warp works on PYR_ROWS consecutive interior rows; a thread on one group of four pixels that
-     * lies fully inside the image.  The 19 px border (and the last 1-3 columns when w % 4 != 0) is filled afterwards for
-     * all levels at once by k_pyramid_borders: the next level's resize never reads a border pixel with a non-zero weight. */
+     * lies fully inside the image.  The border pixels the extractor reads (and the last 1-3 columns when w % 4 != 0) are filled
+     * afterwards for all levels at once by k_pyramid_fringe: the next level's resize never reads a border pixel with a non-zero weight. */
     const int row0 = (blockIdx.y * 8 + threadIdx.y) * PYR_ROWS;   /* interior row */
     if (row0 >= a.h) return;
     const int tx = blockIdx.x * 32 + threadIdx.x;
