@@ -276,9 +276,10 @@ int orbfe_extractor_create(const orbfe_params* p, int device, int width, int hei
     int cap2 = 64;
     while (cap2 < nodeCap) cap2 <<= 1;
     if (cap2 > 2048) {
-        orbfe_set_error("nfeatures too large for the on-chip quadtree (node capacity %d > 2048)", cap2);
+        orbfe_set_error("the on-chip quadtree holds 2048 nodes per level: needs %d here (a level has more than 2048 FAST cells, i.e. more than "
+                        "about 2.5 megapixels, or a per-level feature quota above 2045)", nodeCap);
         delete ex;
-        return ORBFE_E_INVALID;
+        return ORBFE_E_CAPACITY;
     }
     d.nodeCap = cap2;
     d.nCells = (int)cells.size();
