@@ -335,19 +335,28 @@ static __host__ __device__ __forceinline__ bool fast_is_corner_vals(int v, const
  * operand a plain non-negated register: nvcc 12.9 folds a negation into VIMNMX3 on sm_100a and the result
  * loses the sign (found by tools/fast_device_test3.cu: max(m, max(lo, -hi)) returned max(m, lo, hi)). */
 static __host__ __device__ __forceinline__ int fast_score_vals(int v, const int (&r)[16]) {
-    int lo2[16], hi2[16], lo4[16], hi4[16];
-#pragma unroll
-    for (int k = 0; k < 16; k++) { lo2[k] = min(r[k], r[(k + 1) & 15]); hi2[k] = max(r[k], r[(k + 1) & 15]); }
-#pragma unroll
-    for (int k = 0; k < 16; k++) { lo4[k] = min(lo2[k], lo2[(k + 2) & 15]); hi4[k] = max(hi2[k], hi2[(k + 2) & 15]); }
-    int minOfMax = 255, maxOfMin = 0;
+    /* arcs of nine as three runs of three: 16 + 16 three-input min (max) per polarity, then a three-input reduction */
+    int lo3[16], hi3[16];
 #pragma unroll
     for (int k = 0; k < 16; k++) {
-        const int lo9 = min(min(lo4[k], lo4[(k + 4) & 15]), r[(k + 8) & 15]);
-        const int hi9 = max(max(hi4[k], hi4[(k + 4) & 15]), r[(k + 8) & 15]);
-        minOfMax = min(minOfMax, hi9);
-        maxOfMin = max(maxOfMin, lo9);
+        lo3[k] = min(min(r[k], r[(k + 1) & 15]), r[(k + 2) & 15]);
+        hi3[k] = max(max(r[k], r[(k + 1) & 15]), r[(k + 2) & 15]);
     }
+    int lo9[16], hi9[16];
+#pragma unroll
+    for (int k = 0; k < 16; k++) {
+        lo9[k] = min(min(lo3[k], lo3[(k + 3) & 15]), lo3[(k + 6) & 15]);
+        hi9[k] = max(max(hi3[k], hi3[(k + 3) & 15]), hi3[(k + 6) & 15]);
+    }
+    int a[6], b[6];
+#pragma unroll
+    for (int k = 0; k < 5; k++) {
+        a[k] = max(max(lo9[3 * k], lo9[3 * k + 1]), lo9[3 * k + 2]);
+        b[k] = min(min(hi9[3 * k], hi9[3 * k + 1]), hi9[3 * k + 2]);
+    }
+    a[5] = lo9[15]; b[5] = hi9[15];
+    const int maxOfMin = max(max(max(a[0], a[1]), a[2]), max(max(a[3], a[4]), a[5]));
+    const int minOfMax = min(min(min(b[0], b[1]), b[2]), min(min(b[3], b[4]), b[5]));
     const int dark = v - minOfMax, bright = maxOfMin - v;
     return (dark > bright ? dark : bright) - 1;
 }
