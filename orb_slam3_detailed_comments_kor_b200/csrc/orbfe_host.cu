@@ -80,6 +80,7 @@ void orbfe_extractor_destroy(orbfe_extractor* ex) {
     if (!ex) return;
     cudaSetDevice(ex->device);
     if (ex->stream) cudaStreamSynchronize(ex->stream);
+    if (ex->graphExec) cudaGraphExecDestroy(ex->graphExec);
     for (void* p : ex->allocs) cudaFree(p);
     if (ex->hKps) cudaFreeHost(ex->hKps);
     if (ex->hDesc) cudaFreeHost(ex->hDesc);
@@ -122,6 +123,8 @@ int orbfe_extractor_create(const orbfe_params* p, int device, int width, int hei
     ex->stream = nullptr; ex->copyIn = nullptr; ex->copyOut = nullptr;
     ex->hKps = nullptr; ex->hDesc = nullptr; ex->hCount = nullptr; ex->hMono = nullptr;
     ex->profiling = 0; ex->stagePending = 0; ex->stereoPending = 0; ex->launches = 0; ex->batchFrames = 0; ex->bordersValid = 0;
+    ex->graphExec = nullptr; ex->graphLap0 = ex->graphLap1 = 0; ex->graphLaunches = 0; ex->singleGraph = 1;
+    if (const char* e = getenv("ORBFE_SINGLE_FRAME_GRAPH")) ex->singleGraph = atoi(e) != 0;
     memset(ex->ev, 0, sizeof ex->ev);
     memset(ex->stageMs, 0, sizeof ex->stageMs);
     memset(&ex->d, 0, sizeof ex->d);
@@ -597,12 +600,41 @@ int orbfe_extract(orbfe_extractor* ex, const uint8_t* image, int rows, int cols,
     cudaStream_t st = ex->stream;
     ORBFE_CUDA(cudaMemcpy2DAsync(ex->inputStage, cols, image, step, cols, rows, cudaMemcpyHostToDevice, st));
     ex->lastBatch = 1;
-    int rc = orbfe_launch_extract(ex, ex->inputStage, 1, lap0, lap1, st, 0);
-    if (rc) return rc;
-    ORBFE_CUDA(cudaMemcpyAsync(ex->hCount, ex->b.count, sizeof(int), cudaMemcpyDeviceToHost, st));
-    ORBFE_CUDA(cudaMemcpyAsync(ex->hMono, ex->b.mono, sizeof(int), cudaMemcpyDeviceToHost, st));
-    ORBFE_CUDA(cudaMemcpyAsync(ex->hKps, ex->b.kps, (size_t)ex->d.kpCap * sizeof(orbfe_keypoint), cudaMemcpyDeviceToHost, st));
-    ORBFE_CUDA(cudaMemcpyAsync(ex->hDesc, ex->b.desc, (size_t)ex->d.kpCap * 32, cudaMemcpyDeviceToHost, st));
+    /* one frame is sixteen short kernels: launch-bound.  They and the result downloads are captured once per lapping interval
+     * into a CUDA graph and replayed (not while per-stage profiling is on: its events belong to no graph). */
+    const bool useGraph = ex->singleGraph != 0 && ex->profiling == 0;
+    if (useGraph && (!ex->graphExec || ex->graphLap0 != lap0 || ex->graphLap1 != lap1)) {
+        if (ex->graphExec) { cudaGraphExecDestroy(ex->graphExec); ex->graphExec = nullptr; }
+        cudaGraph_t g = nullptr;
+        ORBFE_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+        int rc = orbfe_launch_extract(ex, ex->inputStage, 1, lap0, lap1, st, 0);
+        cudaError_t e = cudaSuccess;
+        if (!rc) e = cudaMemcpyAsync(ex->hCount, ex->b.count, sizeof(int), cudaMemcpyDeviceToHost, st);
+        if (!rc && e == cudaSuccess) e = cudaMemcpyAsync(ex->hMono, ex->b.mono, sizeof(int), cudaMemcpyDeviceToHost, st);
+        if (!rc && e == cudaSuccess) e = cudaMemcpyAsync(ex->hKps, ex->b.kps, (size_t)ex->d.kpCap * sizeof(orbfe_keypoint), cudaMemcpyDeviceToHost, st);
+        if (!rc && e == cudaSuccess) e = cudaMemcpyAsync(ex->hDesc, ex->b.desc, (size_t)ex->d.kpCap * 32, cudaMemcpyDeviceToHost, st);
+        const cudaError_t e2 = cudaStreamEndCapture(st, &g);
+        if (rc) { if (g) cudaGraphDestroy(g); return rc; }
+        if (e != cudaSuccess || e2 != cudaSuccess) { if (g) cudaGraphDestroy(g); return orbfe_cuda_fail(e != cudaSuccess ? e : e2, "graph capture of the single-frame path"); }
+        e = cudaGraphInstantiate(&ex->graphExec, g, 0);
+        cudaGraphDestroy(g);
+        if (e != cudaSuccess) { ex->graphExec = nullptr; return orbfe_cuda_fail(e, "cudaGraphInstantiate"); }
+        ex->graphLap0 = lap0; ex->graphLap1 = lap1;
+        ex->graphLaunches = ex->d.nlevels + 8;
+        ex->launches -= ex->graphLaunches;   /* the capture counted them once without running them */
+    }
+    if (useGraph) {
+        ORBFE_CUDA(cudaGraphLaunch(ex->graphExec, st));
+        ex->launches += ex->graphLaunches;
+        ex->batchFrames = 1; ex->bordersValid = 0;
+    } else {
+        int rc = orbfe_launch_extract(ex, ex->inputStage, 1, lap0, lap1, st, 0);
+        if (rc) return rc;
+        ORBFE_CUDA(cudaMemcpyAsync(ex->hCount, ex->b.count, sizeof(int), cudaMemcpyDeviceToHost, st));
+        ORBFE_CUDA(cudaMemcpyAsync(ex->hMono, ex->b.mono, sizeof(int), cudaMemcpyDeviceToHost, st));
+        ORBFE_CUDA(cudaMemcpyAsync(ex->hKps, ex->b.kps, (size_t)ex->d.kpCap * sizeof(orbfe_keypoint), cudaMemcpyDeviceToHost, st));
+        ORBFE_CUDA(cudaMemcpyAsync(ex->hDesc, ex->b.desc, (size_t)ex->d.kpCap * 32, cudaMemcpyDeviceToHost, st));
+    }
     ORBFE_CUDA(cudaStreamSynchronize(st));
     const int cnt = ex->hCount[0];
     if (n) *n = cnt;

@@ -135,6 +135,8 @@ struct orbfe_extractor {
     long long launches;   /* kernels launched so far by this object */
     int batchFrames;      /* frames of the last batch (chunks of the host pipeline accumulate) */
     int bordersValid;     /* the 19 px pyramid border of those frames has been written (orbfe_materialize_borders) */
+    cudaGraphExec_t graphExec;   /* the single-frame path (orbfe_extract) as a graph, captured per lapping interval */
+    int graphLap0, graphLap1, graphLaunches, singleGraph;
     /* pinned host staging for the host entry points */
     orbfe_keypoint* hKps;
     uint8_t* hDesc;

@@ -1,22 +1,25 @@
-"""Per-stage device time of one 752x480 frame (development aid)."""
-import os, sys, time, ctypes as C
+"""Single-frame latency of orbfe_extract (development aid): python tools/single_frame_probe.py"""
+import os, sys, time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-import numpy as np, torch
-from orb_slam3_detailed_comments_kor_b200 import ORBextractor, synth, _lib
-import bench
-L = _lib.lib()
-img = synth.frame(0, bench.W, bench.H)
-ex = ORBextractor(*bench.PARAMS, width=bench.W, height=bench.H, max_batch=1)
-d = torch.from_numpy(img).cuda(); s = torch.cuda.Stream()
-for _ in range(5): ex(img)
+import numpy as np
+from orb_slam3_detailed_comments_kor_b200 import ORBextractor, synth
+W, H = 752, 480
+ex = ORBextractor(1200, 1.2, 8, 20, 7, width=W, height=H, max_batch=1)
+imgs = [synth.frame(i, W, H) for i in range(8)]
+for i in range(10):
+    ex(imgs[i % 8])
 t = time.perf_counter()
-for _ in range(50): ex(img)
-print("orbfe_extract host call: %.1f us" % ((time.perf_counter() - t) / 50 * 1e6))
+for i in range(200):
+    ex(imgs[i % 8])
+print("graph", os.environ.get("ORBFE_SINGLE_FRAME_GRAPH", "1"), "single-frame latency %.1f us" % ((time.perf_counter() - t) / 200 * 1e6))
+# per-stage device time of one frame (library-side CUDA events)
+import ctypes as C
+from orb_slam3_detailed_comments_kor_b200 import _lib
+L = _lib.lib()
 _lib.check(L.orbfe_set_profiling(ex.handle, 1))
-N = 50
-for _ in range(N):
-    ex.extract_batch_device(d.data_ptr(), 1, (0, 0), s.cuda_stream)
-torch.cuda.synchronize()
-buf = (C.c_double * 8)(); n = C.c_int64(0)
-_lib.check(L.orbfe_stage_times(ex.handle, buf, C.byref(n)))
-print("device us per frame:", {k: round(v / N * 1e3, 1) for k, v in zip(bench.STAGES, buf)}, "sum %.1f" % (sum(buf) / N * 1e3))
+buf = (C.c_double * 8)()
+nl = C.c_int64(0)
+for i in range(50):
+    ex(imgs[i % 8])
+_lib.check(L.orbfe_stage_times(ex.handle, buf, C.byref(nl)))
+print("stage us per frame:", dict(zip(["pyramid", "fast", "blur", "quadtree", "assemble", "orient", "st", "stm"], [round(v * 1000 / 50, 1) for v in buf])))
