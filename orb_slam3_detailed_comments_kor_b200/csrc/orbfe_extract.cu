@@ -882,35 +882,24 @@ __global__ void __launch_bounds__(QT_NT) k_quadtree(const __grid_constant__ ExDe
     const int* cellCount = b.cellCount + f * d.nCells + L.cellBase;
     int nKeys;
     {
-        /* scanA doubles as the per-cell prefix when ncell <= cap, otherwise cells are walked serially */
+        /* scanA doubles as the per-cell prefix; levels with more cells than node slots go through it in slices of `cap` cells */
         int* pre = scanA;
-        if (ncell <= cap) {
-            for (int i = tid; i < ncell; i += QT_NT) pre[i] = cellCount[i];
+        const uint32_t* cand = b.cand + f * d.candCap;
+        const int warp = tid >> 5, lane = tid & 31;
+        nKeys = 0;
+        for (int c0 = 0; c0 < ncell; c0 += cap) {
+            const int m = min(cap, ncell - c0);
+            for (int i = tid; i < m; i += QT_NT) pre[i] = cellCount[c0 + i];
             __syncthreads();
-            nKeys = block_exscan(pre, ncell, s_tmp);
-            const uint32_t* cand = b.cand + f * d.candCap;
-            const int warp = tid >> 5, lane = tid & 31;
-            for (int c = warp; c < ncell; c += QT_NT / 32) {
-                const int n = cellCount[c];
-                const uint32_t* src = cand + b.cells[L.cellBase + c].candBase;
-                for (int i = lane; i < n; i += 32) keys[pre[c] + i] = src[i];
+            const int tot = block_exscan(pre, m, s_tmp);
+            for (int c = warp; c < m; c += QT_NT / 32) {
+                const int n = cellCount[c0 + c];
+                const uint32_t* src = cand + b.cells[L.cellBase + c0 + c].candBase;
+                for (int i = lane; i < n; i += 32) keys[nKeys + pre[c] + i] = src[i];
             }
-        } else {
-            if (tid == 0) {
-                int run = 0;
-                const uint32_t* cand = b.cand + f * d.candCap;
-                for (int c = 0; c < ncell; c++) {
-                    const int n = cellCount[c];
-                    const uint32_t* src = cand + b.cells[L.cellBase + c].candBase;
-                    for (int i = 0; i < n; i++) keys[run + i] = src[i];
-                    run += n;
-                }
-                s_nexp = run;
-            }
+            nKeys += tot;
             __syncthreads();
-            nKeys = s_nexp;
         }
-        __syncthreads();
     }
     if (nKeys == 0) {
         if (tid == 0) *selCount = 0;

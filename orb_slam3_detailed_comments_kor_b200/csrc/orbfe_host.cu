@@ -258,7 +258,7 @@ int orbfe_extractor_create(const orbfe_params* p, int device, int width, int hei
                     dst.push_back(sd);
                 }
         }
-        nodeCap = std::max(nodeCap, std::max(L.selCap, std::max(L.nIni, L.nCols * L.nRows)));
+        nodeCap = std::max(nodeCap, std::max(L.selCap, L.nIni));
         if (l > 0) {
             while (tabs.size() % 4) tabs.push_back(make_uint2(0, 0)); /* k_pyramid_level reads tabX four entries at a time */
             L.tabX = (int)tabs.size();
@@ -279,8 +279,7 @@ int orbfe_extractor_create(const orbfe_params* p, int device, int width, int hei
     int cap2 = 64;
     while (cap2 < nodeCap) cap2 <<= 1;
     if (cap2 > 2048) {
-        orbfe_set_error("the on-chip quadtree holds 2048 nodes per level: needs %d here (a level has more than 2048 FAST cells, i.e. more than "
-                        "about 2.5 megapixels, or a per-level feature quota above 2045)", nodeCap);
+        orbfe_set_error("the on-chip quadtree holds 2048 nodes per level: needs %d here (per-level feature quota above 2045)", nodeCap);
         delete ex;
         return ORBFE_E_CAPACITY;
     }

@@ -33,8 +33,10 @@ SHAPES = {
     "scale15": (701, 499, 14, (700, 1.5, 4, 30, 10), [(0, 350)]),
     "one_level": (322, 242, 15, (400, 1.2, 1, 20, 7), [(0, 0)]),
     "tall": (300, 500, 16, (500, 1.25, 5, 15, 5), [(0, 0)]),
-    # near the size limit of the library (2048 FAST cells on level 0: 56 x 36 cells here) with a large feature budget
+    # a large feature budget (the per-level quota near the 2045 the on-chip quadtree holds) on 2016 cells ...
     "big1980": (1980, 1270, 17, (5000, 1.2, 8, 20, 7), [(0, 1000)]),
+    # ... and the largest image the library takes: 9690 cells on level 0, gathered in slices by the quadtree kernel
+    "max4000": (4000, 3000, 19, (3000, 1.2, 8, 20, 7), [(0, 2000)]),
     # the smallest image the reference's cell grid accepts at 2 levels (a 35 px grid needs > 66 px on the coarsest level)
     "tiny": (96, 84, 18, (100, 1.2, 2, 20, 7), [(0, 0)]),
 }
@@ -194,8 +196,9 @@ def test_host_batch_pipeline_over_several_chunks():
 
 
 def test_capacity_limits_are_refused_loudly():
-    """What the on-chip quadtree cannot hold (more than 2048 cells or nodes on a level) is an error at creation, not a wrong result."""
-    for W, H, nfeat in ((4000, 3000, 3000), (752, 480, 12000), (4001, 480, 1000)):
+    """What the library cannot hold (more than 2048 quadtree nodes on a level, a side above 4000 px) is an error at creation, not
+    a wrong result."""
+    for W, H, nfeat in ((752, 480, 12000), (4001, 480, 1000), (480, 4001, 1000)):
         with pytest.raises(OrbfeError):
             ORBextractor(nfeat, 1.2, 8, 20, 7, width=W, height=H)
 
