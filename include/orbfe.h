@@ -66,8 +66,9 @@ const char* orbfe_version(void);
  * pattern upload — plus everything a GPU needs once: the image shape and the largest batch are fixed here so
  * that no call below allocates.  width/height are the input image size; max_batch >= 1.
  * Limits (ORBFE_E_INVALID / ORBFE_E_CAPACITY at creation, never a wrong result): width, height <= 4000; a per-level feature quota
- * <= 2045 (the quadtree of a level lives in shared memory; nfeatures up to about 9000 at scale 1.2); every level at least 67 px wide
- * and high (the reference divides by zero below that, src/ORBextractor.cc:782-785). */
+ * <= 16381 (nfeatures up to about 75000 at scale 1.2; up to a quota of 2045 the quadtree of a level lives in shared memory, beyond
+ * in global scratch); every level at least 67 px wide and high (the reference divides by zero below that,
+ * src/ORBextractor.cc:782-785). */
 int orbfe_extractor_create(const orbfe_params* params, int device, int width, int height, int max_batch,
                            orbfe_extractor** out);
 void orbfe_extractor_destroy(orbfe_extractor* ex);

@@ -852,8 +852,10 @@ static __device__ __forceinline__ short4 child_box(short4 bx, int c) {
  * position among the nodes created in the previous round.
  * Dynamic smem layout: see the carve-up below (cap = d.nodeCap, a power of two). */
 __global__ void __launch_bounds__(QT_NT) k_quadtree(const __grid_constant__ ExDesc d, ExBuffers b) {
-    extern __shared__ __align__(16) uint8_t smem[];
+    extern __shared__ __align__(16) uint8_t qt_dyn[];
     const int cap = d.nodeCap;
+    /* the node arrays: shared memory, or this CTA's block of b.qtScratch when a level may hold more than 2048 nodes */
+    uint8_t* smem = d.qtScratchBytes ? b.qtScratch + ((size_t)blockIdx.y * d.nlevels + blockIdx.x) * (size_t)d.qtScratchBytes : qt_dyn;
     short4* box0 = reinterpret_cast<short4*>(smem);
     short4* box1 = box0 + cap;
     int* cnt0 = reinterpret_cast<int*>(box1 + cap);
@@ -1291,6 +1293,7 @@ ExBuffers orbfe_shift_frames(const ExBuffers& b, const ExDesc& d, int f0) {
     s.cand += f * d.candCap; s.cellCount += f * d.nCells; s.raw += f * (size_t)d.rawCap; s.rawCount += f * d.nCells;
     s.keys += f * d.candCap; s.keyNode += f * d.candCap;
     s.sel += f * d.kpCap; s.selCount += f * d.nlevels; s.work += f * d.kpCap;
+    if (s.qtScratch) s.qtScratch += f * d.nlevels * (size_t)d.qtScratchBytes;
     s.kps += f * d.kpCap; s.desc += f * d.kpCap * 32; s.count += f; s.mono += f;
     s.uRight += f * d.kpCap; s.depth += f * d.kpCap; s.sadBest += f * d.kpCap;
     s.stTable += f * d.kpCap; s.stBand += f * (d.stBands + 1);

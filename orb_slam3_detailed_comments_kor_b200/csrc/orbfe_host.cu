@@ -278,12 +278,15 @@ int orbfe_extractor_create(const orbfe_params* p, int device, int width, int hei
     }
     int cap2 = 64;
     while (cap2 < nodeCap) cap2 <<= 1;
-    if (cap2 > 2048) {
-        orbfe_set_error("the on-chip quadtree holds 2048 nodes per level: needs %d here (per-level feature quota above 2045)", nodeCap);
+    if (cap2 > 16384) {
+        orbfe_set_error("the quadtree holds 16384 nodes per level: needs %d here (per-level feature quota above 16381)", nodeCap);
         delete ex;
         return ORBFE_E_CAPACITY;
     }
     d.nodeCap = cap2;
+    /* up to 2048 nodes the node arrays of a level live in the CTA's shared memory; beyond (5 x nFeatures initialisation extractors of
+       the monocular KITTI settings: 10000 features) the same arrays are carved out of a global scratch block per (frame, level) */
+    d.qtScratchBytes = cap2 > 2048 ? (int)align_up(orbfe_quadtree_smem_bytes(cap2), 256) : 0;
     d.nCells = (int)cells.size();
     d.candCap = keyTotal;
     d.nStrips = (int)strips.size();
@@ -295,7 +298,7 @@ int orbfe_extractor_create(const orbfe_params* p, int device, int width, int hei
     d.kpCap = selTotal;
     d.pyrSlab = align_up(pyrOff + 256, 256);
     d.blurSlab = align_up(blurOff + 256, 256);
-    ex->quadSmem = orbfe_quadtree_smem_bytes(cap2);
+    ex->quadSmem = d.qtScratchBytes ? 0 : orbfe_quadtree_smem_bytes(cap2);
     {
         int rows = 8, pix = 8;
         for (const CellDesc& c : cells) {
@@ -334,6 +337,8 @@ int orbfe_extractor_create(const orbfe_params* p, int device, int width, int hei
     TRY(dev_alloc(ex, &b.sel, B * d.kpCap));
     TRY(dev_alloc(ex, &b.selCount, B * nl));
     TRY(dev_alloc(ex, &b.work, B * d.kpCap));
+    b.qtScratch = nullptr;
+    if (d.qtScratchBytes) TRY(dev_alloc(ex, &b.qtScratch, B * nl * (size_t)d.qtScratchBytes));
     TRY(dev_alloc(ex, &b.kps, B * d.kpCap));
     TRY(dev_alloc(ex, &b.desc, B * d.kpCap * 32));
     TRY(dev_alloc(ex, &b.count, B));

@@ -46,6 +46,7 @@ struct ExDesc {
     int candCap;      /* candidate slots per frame, all levels */
     int kpCap;        /* selected keypoints per frame, all levels (= sum selCap) */
     int nodeCap;      /* quadtree node capacity (max over levels of selCap, padded) */
+    int qtScratchBytes; /* 0: the node arrays of a level fit in shared memory; else bytes per (frame, level) of b.qtScratch */
     int iniTh, minTh;
     int blurTile0[ORBFE_MAX_LEVELS + 1]; /* first blur tile of each level in the one blur launch; [nlevels] = total */
     int stBands;      /* 8-row bands of the stereo candidate table: (H >> 3) + 1 */
@@ -96,6 +97,7 @@ struct ExBuffers {
     uint16_t* keyNode;   /* [B][candCap]  quadtree scratch: node of each candidate */
     uint32_t* sel;       /* [B][kpCap]    quadtree output, packed like cand, per level at selBase */
     int* selCount;       /* [B][nlevels] */
+    uint8_t* qtScratch;  /* [B][nlevels][qtScratchBytes] node arrays of the quadtree when they do not fit on chip, else NULL */
     uint2* work;         /* [B][kpCap]    (x | y<<16 in level coords, level | slot<<8) in level order */
     orbfe_keypoint* kps; /* [B][kpCap] */
     uint8_t* desc;       /* [B][kpCap][32] */

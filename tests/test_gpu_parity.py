@@ -35,6 +35,9 @@ SHAPES = {
     "tall": (300, 500, 16, (500, 1.25, 5, 15, 5), [(0, 0)]),
     # a large feature budget (the per-level quota near the 2045 the on-chip quadtree holds) on 2016 cells ...
     "big1980": (1980, 1270, 17, (5000, 1.2, 8, 20, 7), [(0, 1000)]),
+    # mpIniORBextractor of the monocular KITTI settings (5 x 2000 features, src/Tracking.cc:1157): 2171 features on level 0, more than
+    # the 2048 quadtree nodes shared memory holds -> the node arrays move to global scratch
+    "kitti_init": (1241, 376, 20, (10000, 1.2, 8, 20, 7), [(0, 0)]),
     # ... and the largest image the library takes: 9690 cells on level 0, gathered in slices by the quadtree kernel
     "max4000": (4000, 3000, 19, (3000, 1.2, 8, 20, 7), [(0, 2000)]),
     # the smallest image the reference's cell grid accepts at 2 levels (a 35 px grid needs > 66 px on the coarsest level)
@@ -196,9 +199,9 @@ def test_host_batch_pipeline_over_several_chunks():
 
 
 def test_capacity_limits_are_refused_loudly():
-    """What the library cannot hold (more than 2048 quadtree nodes on a level, a side above 4000 px) is an error at creation, not
+    """What the library cannot hold (more than 16384 quadtree nodes on a level, a side above 4000 px) is an error at creation, not
     a wrong result."""
-    for W, H, nfeat in ((752, 480, 12000), (4001, 480, 1000), (480, 4001, 1000)):
+    for W, H, nfeat in ((752, 480, 80000), (4001, 480, 1000), (480, 4001, 1000)):
         with pytest.raises(OrbfeError):
             ORBextractor(nfeat, 1.2, 8, 20, 7, width=W, height=H)
 
