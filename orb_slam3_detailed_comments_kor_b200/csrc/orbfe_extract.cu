@@ -851,11 +851,12 @@ static __device__ __forceinline__ short4 child_box(short4 bx, int c) {
  * equal-sized nodes in the final partial rounds are broken by creation order (latest first) = ascending list
  * position among the nodes created in the previous round.
  * Dynamic smem layout: see the carve-up below (cap = d.nodeCap, a power of two). */
+template <bool SCRATCH>   /* SCRATCH: the node arrays live in b.qtScratch (global) instead of shared memory */
 __global__ void __launch_bounds__(QT_NT) k_quadtree(const __grid_constant__ ExDesc d, ExBuffers b) {
     extern __shared__ __align__(16) uint8_t qt_dyn[];
     const int cap = d.nodeCap;
     /* the node arrays: shared memory, or this CTA's block of b.qtScratch when a level may hold more than 2048 nodes */
-    uint8_t* smem = d.qtScratchBytes ? b.qtScratch + ((size_t)blockIdx.y * d.nlevels + blockIdx.x) * (size_t)d.qtScratchBytes : qt_dyn;
+    uint8_t* smem = SCRATCH ? b.qtScratch + ((size_t)blockIdx.y * d.nlevels + blockIdx.x) * (size_t)d.qtScratchBytes : qt_dyn;
     short4* box0 = reinterpret_cast<short4*>(smem);
     short4* box1 = box0 + cap;
     int* cnt0 = reinterpret_cast<int*>(box1 + cap);
@@ -1280,7 +1281,7 @@ int orbfe_collect_stage_times(orbfe_extractor* ex);
 int orbfe_blur_tiles(int w, int h) { return ((w + BLUR_TW - 1) / BLUR_TW) * ((h + BLUR_TH - 1) / BLUR_TH); }
 
 int orbfe_configure_kernels(int quadSmem, int fastSmem) {
-    ORBFE_CUDA(cudaFuncSetAttribute(k_quadtree, cudaFuncAttributeMaxDynamicSharedMemorySize, quadSmem));
+    ORBFE_CUDA(cudaFuncSetAttribute(k_quadtree<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, quadSmem));
     ORBFE_CUDA(cudaFuncSetAttribute(k_fast_cells_list, cudaFuncAttributeMaxDynamicSharedMemorySize, fastSmem));
     return 0;
 }
@@ -1343,7 +1344,8 @@ int orbfe_launch_extract(orbfe_extractor* ex, const uint8_t* d_images, int nfram
     STAGE_MARK();
     k_blur7<<<dim3(d.blurTile0[d.nlevels], nframes), 256, 0, st>>>(d, xb);
     STAGE_MARK();
-    k_quadtree<<<dim3(d.nlevels, nframes), QT_NT, ex->quadSmem, st>>>(d, xb);
+    if (d.qtScratchBytes) k_quadtree<true><<<dim3(d.nlevels, nframes), QT_NT, 0, st>>>(d, xb);
+    else k_quadtree<false><<<dim3(d.nlevels, nframes), QT_NT, ex->quadSmem, st>>>(d, xb);
     STAGE_MARK();
     k_assemble<<<nframes, AS_NT, 0, st>>>(d, xb, lap0, lap1);
     STAGE_MARK();
