@@ -32,6 +32,7 @@
 #define PJ_ROWS 48
 #define PJ_CELLS (PJ_COLS * PJ_ROWS)
 #define PJ_PENDING (-1)
+#define PJ_FRONT 2048   /* only the earliest PJ_FRONT unresolved queries take part in a round */
 
 struct PjSmem {
     int cellEnd[2 * PJ_CELLS];      /* end of each cell's run in `sorted` (start = end of the cell before) */
@@ -203,15 +204,25 @@ __global__ void __launch_bounds__(PJ_NT) k_search_by_projection(int maxKp, const
     }
     __syncthreads();
 
-    /* ---- rounds ---- */
+    /* ---- rounds ----
+     * A round costs (participants x window); a query behind a long chain of earlier ones over the same keypoints would pay that
+     * every round while it waits.  So only the earliest PJ_FRONT unresolved queries take part: the rule of step B needs the stamps
+     * of all EARLIER unresolved queries, and those are inside the front by construction. */
+    __shared__ int s_front;
+    int myFirst = tid;   /* my first query that may still be unresolved (I own tid, tid + PJ_NT, ...) */
     for (;;) {
         for (int i = tid; i < fr.n; i += PJ_NT) {
             s.owner[i] = INT_MAX;
             if (takenB[i] & 2) takenB[i] = 1;
         }
+        if (tid == 0) s_front = INT_MAX;
         __syncthreads();
+        while (myFirst < nq && status[myFirst * 7] != PJ_PENDING) myFirst += PJ_NT;
+        if (myFirst < nq) atomicMin(&s_front, myFirst);
+        __syncthreads();
+        const int limit = s_front > INT_MAX - PJ_FRONT ? INT_MAX : s_front + PJ_FRONT;
         /* A. stamps */
-        for (int q = tid; q < nq; q += PJ_NT) {
+        for (int q = myFirst; q < nq && q < limit; q += PJ_NT) {
             if (status[q * 7] != PJ_PENDING) continue;
             const orbfe_proj_query p = qs[q];
             if (p.flags & (ORBFE_PQ_AFTER_LEFT | ORBFE_PQ_NEEDS_LEFT_WINDOW))
@@ -229,7 +240,8 @@ __global__ void __launch_bounds__(PJ_NT) k_search_by_projection(int maxKp, const
         __syncthreads();
         /* B. scan, decide */
         int pending = 0;
-        for (int q = tid; q < nq; q += PJ_NT) {
+        for (int q = myFirst; q < nq; q += PJ_NT) {
+            if (q >= limit) { pending++; break; }   /* behind the front: waits */
             if (status[q * 7] != PJ_PENDING) continue;
             const orbfe_proj_query p = qs[q];
             if (p.flags & (ORBFE_PQ_AFTER_LEFT | ORBFE_PQ_NEEDS_LEFT_WINDOW)) {

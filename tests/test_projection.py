@@ -92,6 +92,17 @@ def test_gpu_search_matches_oracle_and_goldens():
         bad = np.nonzero((_as_matrix(out) != _as_matrix(want)).any(1))[0]
         assert bad.size == 0, (kw, bad[:5], out[bad[:3]], want[bad[:3]])
         assert np.array_equal(taken, wtaken) and nm == wnm, kw
+    # the worst case for the speculative rounds: every map point has the same descriptor and sees every keypoint, so each one
+    # depends on all the ones before it (one query resolves per round); must still be exact, and finish
+    c = PC.make_case(seed=33, n=1000, nq=1500, th=1.0)
+    c["qdesc"][:] = c["desc"][7]
+    c["queries"]["radius"] = 2000.0
+    c["queries"]["min_level"], c["queries"]["max_level"] = 0, -1
+    c["queries"]["flags"] = PC.PQ_BLOCKS | PC.PQ_BEST_ONLY
+    c["th_high"] = np.array([256], np.int32)               # every map point takes the best keypoint that is left
+    want, wtaken, wnm = _run(O.search_by_projection, c)
+    out, taken, nm = _run(P.search_by_projection, c)
+    assert np.array_equal(_as_matrix(out), _as_matrix(want)) and np.array_equal(taken, wtaken) and nm == wnm and nm > 800
     # no queries, and a frame beyond the capacity
     c = PC.make_case(seed=27, n=50, nq=4)
     out, taken, nm = P.search_by_projection(c["kps"], c["desc"], c["queries"][:0], c["qdesc"][:0], c["grid"])
