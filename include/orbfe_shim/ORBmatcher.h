@@ -5,7 +5,7 @@
  * brute-force top-2 core that SearchByBoW's inner loops perform (src/ORBmatcher.cc:311-375, 870-908), and free
  * functions carrying the bodies of Frame::ComputeStereoMatches / ComputeStereoFishEyeMatches's matching step and of
  * SearchByProjection(Frame&, vpMapPoints, th, ...) (src/ORBmatcher.cc:44-214).
- * The BoW-node gating and the other projection overloads stay in the reference's ORBmatcher.cc. */
+ * The full SearchByBoW / SearchForTriangulation / Fuse searches are C-ABI entry points (include/orbfe.h). */
 #ifndef ORBFE_SHIM_ORBMATCHER_H
 #define ORBFE_SHIM_ORBMATCHER_H
 
