@@ -239,20 +239,23 @@ int orbfe_bow_device_views(orbfe_vocabulary* v, const int32_t** d_feat_word, con
  * frame d_pair_f[p].  d_has_map_point: nonzero iff vpMapPointsKF[row] && !isBad() (NULL = all).  d_match_f[p*row_stride + i] = the
  * keyframe row whose map point goes to vpMapPointMatches[i], or -1; d_kf_out (may be NULL) [p*row_stride + row]: best1 / best2 /
  * idx of that keyframe row's scan, accepted = 1 kept, 2 removed by the rotation check; d_nmatches[p] (may be NULL) = return value.
+ * d_n_left (per frame, NULL = all -1) is F.Nleft: on a fisheye rig (>= 0) the frame's rows >= Nleft are the right camera's and compete
+ * separately (:330-358); the right-camera best is then assigned too whenever it and the left best are <= TH_LOW (:388-416).
  * th_low = ORBmatcher::TH_LOW (50).  kf_kf != 0 selects ORBmatcher::SearchByBoW(KeyFrame *pKF1, KeyFrame *pKF2, vpMatches12)
  * (src/ORBmatcher.cc:823-963, the NLeft == -1 path): rows of the second keyframe without a map point are no candidates either
  * (d_has_map_point is read for both frames) and the threshold is bestDist1 < TH_LOW; vpMatches12[row1] = vpMapPoints2[d_kf_out[row1].idx]
  * where accepted == 1.  At most 4096 features per frame. */
 int orbfe_search_by_bow_device(int device, int npairs, int max_features, const int32_t* d_pair_kf, const int32_t* d_pair_f, const uint8_t* d_desc,
                                const orbfe_keypoint* d_kps, int row_stride, const int32_t* d_fv_nodes, const int32_t* d_fv_starts, const int32_t* d_fv_feats,
-                               const int32_t* d_fv_count, const uint8_t* d_has_map_point, int th_low, float nnratio, int check_orientation, int kf_kf,
-                               int32_t* d_match_f, orbfe_match* d_kf_out, int32_t* d_nmatches, void* stream);
+                               const int32_t* d_fv_count, const uint8_t* d_has_map_point, const int32_t* d_n_left, int th_low, float nnratio,
+                               int check_orientation, int kf_kf, int32_t* d_match_f, orbfe_match* d_kf_out, int32_t* d_nmatches, void* stream);
 /* One pair over host memory; the fv_* arrays are those orbfe_bow_result / orbfe_bow_transform return for the two frames
- * (has_map_point_f is read only with kf_kf; NULL = all). */
+ * (has_map_point_f is read only with kf_kf; NULL = all; n_left_f = F.Nleft, -1 for one camera). */
 int orbfe_search_by_bow(int device, const uint8_t* desc_kf, const orbfe_keypoint* kps_kf, int n_kf, const int32_t* fv_nodes_kf, const int32_t* fv_starts_kf,
                         const int32_t* fv_feats_kf, int nfv_kf, const uint8_t* has_map_point, const uint8_t* desc_f, const orbfe_keypoint* kps_f, int n_f,
                         const int32_t* fv_nodes_f, const int32_t* fv_starts_f, const int32_t* fv_feats_f, int nfv_f, const uint8_t* has_map_point_f,
-                        int th_low, float nnratio, int check_orientation, int kf_kf, int32_t* match_f, orbfe_match* kf_out, int* nmatches);
+                        int n_left_f, int th_low, float nnratio, int check_orientation, int kf_kf, int32_t* match_f, orbfe_match* kf_out,
+                        int* nmatches);
 
 /* Replaces ORBmatcher::SearchForTriangulation(KeyFrame *pKF1, KeyFrame *pKF2, cv::Mat F12, vMatchedPairs, bOnlyStereo, bCoarse)
  * (src/ORBmatcher.cc:965-1206; LocalMapping::CreateNewMapPoints) for pinhole keyframes without a second camera, for batches of

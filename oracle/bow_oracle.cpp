@@ -129,8 +129,8 @@ int orc_bow_transform(const orc_vocabulary* voc, const uint8_t* features, int n,
  * best1/best2/idx and accepted (1 kept, 2 removed by the rotation histogram).  Returns nmatches. */
 int orc_search_by_bow(const uint8_t* desc_kf, const orc_keypoint* kps_kf, int n_kf, const int32_t* nodes_kf, const int32_t* starts_kf, const int32_t* feats_kf,
                       int nfv_kf, const uint8_t* has_map_point, const uint8_t* desc_f, const orc_keypoint* kps_f, int n_f, const int32_t* nodes_f,
-                      const int32_t* starts_f, const int32_t* feats_f, int nfv_f, const uint8_t* has_map_point_f, int th_low, float nnratio,
-                      int check_orientation, int kf_kf, int32_t* match_f, orc_match* kf_out) {
+                      const int32_t* starts_f, const int32_t* feats_f, int nfv_f, const uint8_t* has_map_point_f, int n_left_f, int th_low,
+                      float nnratio, int check_orientation, int kf_kf, int32_t* match_f, orc_match* kf_out) {
     const int HISTO_LENGTH = 30;
     for (int i = 0; i < n_f; i++) match_f[i] = -1;
     if (kf_out) for (int i = 0; i < n_kf; i++) { kf_out[i].best1 = 256; kf_out[i].best2 = 256; kf_out[i].idx = -1; kf_out[i].accepted = 0; }
@@ -145,13 +145,32 @@ int orc_search_by_bow(const uint8_t* desc_kf, const orc_keypoint* kps_kf, int n_
                 if (has_map_point && !has_map_point[realIdxKF]) continue;
                 const uint8_t* dKF = desc_kf + (size_t)realIdxKF * 32;
                 int bestDist1 = 256, bestIdxF = -1, bestDist2 = 256;
+                int bestDist1R = 256, bestIdxFR = -1, bestDist2R = 256;
                 for (int iF = starts_f[Fit]; iF < starts_f[Fit + 1]; iF++) {
                     const int realIdxF = feats_f[iF];
                     if (match_f[realIdxF] >= 0) continue;
                     if (kf_kf && has_map_point_f && !has_map_point_f[realIdxF]) continue;   /* :886-892 (keyframe-keyframe overload) */
                     const int dist = orc_descriptor_distance(dKF, desc_f + (size_t)realIdxF * 32);
-                    if (dist < bestDist1) { bestDist2 = bestDist1; bestDist1 = dist; bestIdxF = realIdxF; }
-                    else if (dist < bestDist2) { bestDist2 = dist; }
+                    if (n_left_f < 0 || kf_kf) {                                            /* F.Nleft == -1, :314-329 */
+                        if (dist < bestDist1) { bestDist2 = bestDist1; bestDist1 = dist; bestIdxF = realIdxF; }
+                        else if (dist < bestDist2) { bestDist2 = dist; }
+                    } else {                                                                /* :330-358 */
+                        if (realIdxF < n_left_f && dist < bestDist1) { bestDist2 = bestDist1; bestDist1 = dist; bestIdxF = realIdxF; }
+                        else if (realIdxF < n_left_f && dist < bestDist2) { bestDist2 = dist; }
+                        if (realIdxF >= n_left_f && dist < bestDist1R) { bestDist2R = bestDist1R; bestDist1R = dist; bestIdxFR = realIdxF; }
+                        else if (realIdxF >= n_left_f && dist < bestDist2R) { bestDist2R = dist; }
+                    }
+                }
+                if (!kf_kf && n_left_f >= 0 && bestDist1 <= th_low && bestDist1R <= th_low) {   /* :388-416, `|| true` */
+                    match_f[bestIdxFR] = realIdxKF;
+                    if (check_orientation) {
+                        float rot = kps_kf[realIdxKF].angle - kps_f[bestIdxFR].angle;
+                        if (rot < 0.0) rot += 360.0f;
+                        int bin = (int)std::round(rot * factor);
+                        if (bin == HISTO_LENGTH) bin = 0;
+                        if (bin >= 0 && bin < HISTO_LENGTH) rotHist[bin].push_back(bestIdxFR);
+                    }
+                    nmatches++;
                 }
                 bool ok = false;
                 if ((kf_kf ? bestDist1 < th_low : bestDist1 <= th_low) && static_cast<float>(bestDist1) < nnratio * static_cast<float>(bestDist2)) {

@@ -67,7 +67,7 @@ def lib():
     L.orc_vocabulary_destroy.argtypes = [vp]
     L.orc_vocabulary_words.argtypes = [vp]
     L.orc_bow_transform.argtypes = [vp, vp, C.c_int, C.c_int, vp, vp, vp, vp, vp, vp, vp, vp, vp]
-    L.orc_search_by_bow.argtypes = [vp, vp, C.c_int, vp, vp, vp, C.c_int, vp, vp, vp, C.c_int, vp, vp, vp, C.c_int, vp, C.c_int, C.c_float, C.c_int, C.c_int, vp, vp]
+    L.orc_search_by_bow.argtypes = [vp, vp, C.c_int, vp, vp, vp, C.c_int, vp, vp, vp, C.c_int, vp, vp, vp, C.c_int, vp, C.c_int, C.c_int, C.c_float, C.c_int, C.c_int, vp, vp]
     L.orc_search_by_bow.restype = C.c_int
     L.orc_search_for_triangulation.argtypes = [vp, vp, vp, vp, C.c_int, vp, vp, vp, C.c_int, vp, vp, vp, vp, C.c_int, vp, vp, vp, C.c_int, vp, vp, vp, vp,
                                                C.c_int, C.c_int, C.c_int, C.c_int, vp]
@@ -274,7 +274,7 @@ def _fv_arrays(feat_vec):
 
 
 def search_by_bow(desc_kf, kps_kf, fv_kf, has_map_point, desc_f, kps_f, fv_f, th_low=50, nnratio=0.7, check_orientation=True, kf_kf=False,
-                  has_map_point_f=None):
+                  has_map_point_f=None, n_left_f=-1):
     """ORBmatcher::SearchByBoW(pKF, F, vpMapPointMatches); fv_* = {node: rows} dicts.  Returns (match_f, kf_out, nmatches)."""
     desc_kf = np.ascontiguousarray(desc_kf, np.uint8); desc_f = np.ascontiguousarray(desc_f, np.uint8)
     kps_kf = np.ascontiguousarray(kps_kf, KP_DTYPE); kps_f = np.ascontiguousarray(kps_f, KP_DTYPE)
@@ -285,7 +285,7 @@ def search_by_bow(desc_kf, kps_kf, fv_kf, has_map_point, desc_f, kps_f, fv_f, th
     match_f = np.zeros(max(desc_f.shape[0], 1), np.int32)
     kf_out = np.zeros(max(desc_kf.shape[0], 1), MATCH_DTYPE)
     nm = lib().orc_search_by_bow(_ptr(desc_kf), _ptr(kps_kf), desc_kf.shape[0], _ptr(na), _ptr(sa), _ptr(fa), len(na), _ptr(mp) if mp is not None else None,
-                                 _ptr(desc_f), _ptr(kps_f), desc_f.shape[0], _ptr(nb), _ptr(sb), _ptr(fb), len(nb), _ptr(mpf) if mpf is not None else None, th_low, nnratio,
+                                 _ptr(desc_f), _ptr(kps_f), desc_f.shape[0], _ptr(nb), _ptr(sb), _ptr(fb), len(nb), _ptr(mpf) if mpf is not None else None, int(n_left_f), th_low, nnratio,
                                  int(check_orientation), int(kf_kf), _ptr(match_f), _ptr(kf_out))
     return match_f[:desc_f.shape[0]], kf_out[:desc_kf.shape[0]], nm
 

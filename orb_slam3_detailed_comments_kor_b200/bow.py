@@ -79,7 +79,7 @@ def _fv_arrays(feat_vec):
 
 
 def search_by_bow(desc_kf, kps_kf, fv_kf, has_map_point, desc_f, kps_f, fv_f, th_low=50, nnratio=0.7, check_orientation=True, device=0,
-                  kf_kf=False, has_map_point_f=None):
+                  kf_kf=False, has_map_point_f=None, n_left_f=-1):
     """ORBmatcher::SearchByBoW(KeyFrame*, Frame&, vpMapPointMatches) (src/ORBmatcher.cc:269-470) — or, with kf_kf, the
     keyframe-keyframe overload (:823-963) — for one pair on the host; fv_* are the feat_vec dicts of ORBVocabulary.transform.
     Returns (match_f[nF] keyframe row or -1, kf_out, nmatches)."""
@@ -94,7 +94,8 @@ def search_by_bow(desc_kf, kps_kf, fv_kf, has_map_point, desc_f, kps_f, fv_f, th
     nm = C.c_int(0)
     check(_lib.lib().orbfe_search_by_bow(device, ptr(desc_kf), ptr(kps_kf), desc_kf.shape[0], ptr(na), ptr(sa), ptr(fa), len(na),
                                          ptr(mp) if mp is not None else None, ptr(desc_f), ptr(kps_f), desc_f.shape[0], ptr(nb), ptr(sb), ptr(fb), len(nb),
-                                         ptr(mpf) if mpf is not None else None, th_low, C.c_float(nnratio), int(check_orientation), int(kf_kf),
+                                         ptr(mpf) if mpf is not None else None, int(n_left_f), th_low, C.c_float(nnratio), int(check_orientation),
+                                         int(kf_kf),
                                          ptr(match_f), ptr(kf_out), C.byref(nm)))
     return match_f[:desc_f.shape[0]], kf_out[:desc_kf.shape[0]], nm.value
 

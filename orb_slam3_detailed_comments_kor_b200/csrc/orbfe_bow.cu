@@ -212,14 +212,16 @@ struct SbSmem {
 __global__ void __launch_bounds__(SB_NT) k_search_by_bow(int maxF, const int* __restrict__ pairKf, const int* __restrict__ pairF, const uint4* __restrict__ desc,
                                                          const orbfe_keypoint* __restrict__ kps, int rowStride, const int* __restrict__ fvNodes,
                                                          const int* __restrict__ fvStarts, const int* __restrict__ fvFeats, const int* __restrict__ fvCount,
-                                                         const uint8_t* __restrict__ hasMp, int thLow, float nnratio, int checkOri, int kfkf, int* __restrict__ matchF,
-                                                         orbfe_match* __restrict__ kfOut, int* __restrict__ nmatches) {
+                                                         const uint8_t* __restrict__ hasMp, const int* __restrict__ nLeftAll, int thLow, float nnratio,
+                                                         int checkOri, int kfkf, int* __restrict__ matchF, orbfe_match* __restrict__ kfOut,
+                                                         int* __restrict__ nmatches) {
     __shared__ SbSmem s;
     const int tid = threadIdx.x, pr = blockIdx.x;
     const int a = pairKf[pr], b = pairF[pr];
     const int* nodesA = fvNodes + (size_t)a * maxF; const int* startsA = fvStarts + (size_t)a * (maxF + 1); const int* featsA = fvFeats + (size_t)a * maxF;
     const int* nodesB = fvNodes + (size_t)b * maxF; const int* startsB = fvStarts + (size_t)b * (maxF + 1); const int* featsB = fvFeats + (size_t)b * maxF;
     const int nnA = fvCount[a], nnB = fvCount[b];
+    const int nLeftF = (nLeftAll && !kfkf) ? nLeftAll[b] : -1;   /* F.Nleft: rows >= it belong to the right camera of a fisheye rig */
     const int nq = nnA ? startsA[nnA] : 0;                       /* keyframe features that sit in the feature vector */
     const uint4* descA = desc + (size_t)a * rowStride * 2; const uint4* descB = desc + (size_t)b * rowStride * 2;
     int* mF = matchF + (size_t)pr * rowStride;
@@ -267,26 +269,40 @@ __global__ void __launch_bounds__(SB_NT) k_search_by_bow(int maxF, const int* __
             const int rowA = featsA[q];
             const uint4 qa = __ldg(descA + 2 * rowA), qb = __ldg(descA + 2 * rowA + 1);
             int best1 = 256, best2 = 256, bestIdx = -1;
+            int best1R = 256, best2R = 256, bestIdxR = -1;        /* fisheye rig: the frame's right-camera rows compete separately (:330-358) */
             for (int j = rg & 0xFFFF; j < (int)(rg >> 16); j++) {
                 const int row = featsB[j];
                 if (takenB[row] & 1) continue;                    /* if(vpMapPointMatches[realIdxF]) continue; */
                 const int dist = bow_ham(qa, qb, __ldg(descB + 2 * row), __ldg(descB + 2 * row + 1));
-                if (dist < best1) { best2 = best1; best1 = dist; bestIdx = row; }
-                else if (dist < best2) best2 = dist;
+                if (nLeftF < 0 || row < nLeftF) {
+                    if (dist < best1) { best2 = best1; best1 = dist; bestIdx = row; }
+                    else if (dist < best2) best2 = dist;
+                } else {
+                    if (dist < best1R) { best2R = best1R; best1R = dist; bestIdxR = row; }
+                    else if (dist < best2R) best2R = dist;
+                }
             }
+            const int reach = nLeftF < 0 ? best2 : max(best2, best2R);
             bool blocked = false;
             for (int j = rg & 0xFFFF; j < (int)(rg >> 16) && !blocked; j++) {
                 const int row = featsB[j];
                 if ((takenB[row] & 1) || s.owner[row] >= q) continue;
-                if (bow_ham(qa, qb, __ldg(descB + 2 * row), __ldg(descB + 2 * row + 1)) <= best2) blocked = true;
+                if (bow_ham(qa, qb, __ldg(descB + 2 * row), __ldg(descB + 2 * row + 1)) <= reach) blocked = true;
             }
             if (blocked) { pending++; continue; }
-            const bool ok = bestIdx >= 0 && (kfkf ? best1 < thLow : best1 <= thLow) && (float)best1 < nnratio * (float)best2;
+            const bool th1 = bestIdx >= 0 && (kfkf ? best1 < thLow : best1 <= thLow);
+            const bool ok = th1 && (float)best1 < nnratio * (float)best2;
+            /* :388-416: inside `if(bestDist1<=TH_LOW)`, the right-camera best is taken whenever it is <= TH_LOW (`|| true`) */
+            const bool okR = !kfkf && nLeftF >= 0 && th1 && bestIdxR >= 0 && best1R <= thLow;
             stateB[q] = 1;
             if (ko) { orbfe_match m; m.best1 = best1; m.best2 = best2; m.idx = bestIdx; m.accepted = ok ? 1 : 0; ko[rowA] = m; }
             if (ok) {
                 mF[bestIdx] = rowA;
                 atomicOr(&s.taken[bestIdx >> 2], 2u << (8 * (bestIdx & 3)));
+            }
+            if (okR) {
+                mF[bestIdxR] = rowA;
+                atomicOr(&s.taken[bestIdxR >> 2], 2u << (8 * (bestIdxR & 3)));
             }
         }
         if (__syncthreads_count(pending) == 0) break;
@@ -619,15 +635,15 @@ int orbfe_bow_device_views(orbfe_vocabulary* v, const int32_t** d_feat_word, con
 
 int orbfe_search_by_bow_device(int device, int npairs, int max_features, const int32_t* d_pair_kf, const int32_t* d_pair_f, const uint8_t* d_desc,
                                const orbfe_keypoint* d_kps, int row_stride, const int32_t* d_fv_nodes, const int32_t* d_fv_starts, const int32_t* d_fv_feats,
-                               const int32_t* d_fv_count, const uint8_t* d_has_map_point, int th_low, float nnratio, int check_orientation, int kf_kf,
-                               int32_t* d_match_f, orbfe_match* d_kf_out, int32_t* d_nmatches, void* stream) {
+                               const int32_t* d_fv_count, const uint8_t* d_has_map_point, const int32_t* d_n_left, int th_low, float nnratio,
+                               int check_orientation, int kf_kf, int32_t* d_match_f, orbfe_match* d_kf_out, int32_t* d_nmatches, void* stream) {
     if (npairs < 1 || !d_pair_kf || !d_pair_f || !d_desc || !d_fv_nodes || !d_fv_starts || !d_fv_feats || !d_fv_count || !d_match_f || row_stride < 1 ||
         (check_orientation && !d_kps)) { orbfe_set_error("bad argument"); return ORBFE_E_INVALID; }
     if (max_features < 1 || max_features > BOW_MAXF || row_stride > BOW_MAXF) { orbfe_set_error("at most %d features per frame", BOW_MAXF); return ORBFE_E_CAPACITY; }
     if ((uintptr_t)d_desc & 15) { orbfe_set_error("descriptor array must be 16-byte aligned"); return ORBFE_E_INVALID; }
     ORBFE_CUDA(cudaSetDevice(device));
     k_search_by_bow<<<npairs, SB_NT, 0, (cudaStream_t)stream>>>(max_features, d_pair_kf, d_pair_f, (const uint4*)d_desc, d_kps, row_stride, d_fv_nodes, d_fv_starts,
-                                                                d_fv_feats, d_fv_count, d_has_map_point, th_low, nnratio, check_orientation ? 1 : 0, kf_kf ? 1 : 0, d_match_f,
+                                                                d_fv_feats, d_fv_count, d_has_map_point, d_n_left, th_low, nnratio, check_orientation ? 1 : 0, kf_kf ? 1 : 0, d_match_f,
                                                                 d_kf_out, d_nmatches);
     ORBFE_CUDA(cudaGetLastError());
     return ORBFE_OK;
@@ -637,7 +653,8 @@ int orbfe_search_by_bow_device(int device, int npairs, int max_features, const i
 int orbfe_search_by_bow(int device, const uint8_t* desc_kf, const orbfe_keypoint* kps_kf, int n_kf, const int32_t* fv_nodes_kf, const int32_t* fv_starts_kf,
                         const int32_t* fv_feats_kf, int nfv_kf, const uint8_t* has_map_point, const uint8_t* desc_f, const orbfe_keypoint* kps_f, int n_f,
                         const int32_t* fv_nodes_f, const int32_t* fv_starts_f, const int32_t* fv_feats_f, int nfv_f, const uint8_t* has_map_point_f,
-                        int th_low, float nnratio, int check_orientation, int kf_kf, int32_t* match_f, orbfe_match* kf_out, int* nmatches) {
+                        int n_left_f, int th_low, float nnratio, int check_orientation, int kf_kf, int32_t* match_f, orbfe_match* kf_out,
+                        int* nmatches) {
     if (n_kf < 0 || n_f < 0 || nfv_kf < 0 || nfv_f < 0 || !match_f || (n_kf && !desc_kf) || (n_f && !desc_f) || (check_orientation && (!kps_kf || !kps_f)) ||
         (nfv_kf && (!fv_nodes_kf || !fv_starts_kf || !fv_feats_kf)) || (nfv_f && (!fv_nodes_f || !fv_starts_f || !fv_feats_f))) { orbfe_set_error("bad argument"); return ORBFE_E_INVALID; }
     const int S = std::max(std::max(n_kf, n_f), 1);
@@ -672,23 +689,25 @@ int orbfe_search_by_bow(int device, const uint8_t* desc_kf, const orbfe_keypoint
         memcpy(hFeats.data() + S, fv_feats_f, (size_t)fv_starts_f[nfv_f] * 4);
     }
     hCount[0] = nfv_kf; hCount[1] = nfv_f; hPair[0] = 0; hPair[1] = 1;
+    const int32_t hLeft[2] = {-1, n_left_f < 0 ? -1 : n_left_f};
     size_t off = 0;
     auto take = [&](size_t bytes) { const size_t o = off; off += (bytes + 255) & ~(size_t)255; return o; };
     const size_t oDesc = take(hDesc.size()), oKps = take(hKps.size() * sizeof(orbfe_keypoint)), oMp = take(hMp.size()), oNodes = take(hNodes.size() * 4);
     const size_t oStarts = take(hStarts.size() * 4), oFeats = take(hFeats.size() * 4), oCount = take(8), oPair = take(8), oMatch = take((size_t)S * 4);
-    const size_t oKf = take((size_t)S * sizeof(orbfe_match)), oNm = take(4);
+    const size_t oKf = take((size_t)S * sizeof(orbfe_match)), oNm = take(4), oLeft = take(8);
     uint8_t* d = nullptr;
     ORBFE_CUDA(cudaMalloc((void**)&d, off));
     cudaError_t e = cudaMemcpy(d + oDesc, hDesc.data(), hDesc.size(), cudaMemcpyHostToDevice);
 #define SB_UP(o, v, bytes) if (e == cudaSuccess) e = cudaMemcpy(d + (o), (v), (bytes), cudaMemcpyHostToDevice)
     SB_UP(oKps, hKps.data(), hKps.size() * sizeof(orbfe_keypoint)); SB_UP(oMp, hMp.data(), hMp.size()); SB_UP(oNodes, hNodes.data(), hNodes.size() * 4);
     SB_UP(oStarts, hStarts.data(), hStarts.size() * 4); SB_UP(oFeats, hFeats.data(), hFeats.size() * 4); SB_UP(oCount, hCount.data(), 8); SB_UP(oPair, hPair.data(), 8);
+    SB_UP(oLeft, hLeft, 8);
 #undef SB_UP
     int rc = ORBFE_OK;
     if (e == cudaSuccess)
         rc = orbfe_search_by_bow_device(device, 1, S, (const int32_t*)(d + oPair), (const int32_t*)(d + oPair) + 1, d + oDesc, (const orbfe_keypoint*)(d + oKps), S,
                                         (const int32_t*)(d + oNodes), (const int32_t*)(d + oStarts), (const int32_t*)(d + oFeats), (const int32_t*)(d + oCount),
-                                        d + oMp, th_low, nnratio, check_orientation, kf_kf, (int32_t*)(d + oMatch), (orbfe_match*)(d + oKf), (int32_t*)(d + oNm), nullptr);
+                                        d + oMp, (const int32_t*)(d + oLeft), th_low, nnratio, check_orientation, kf_kf, (int32_t*)(d + oMatch), (orbfe_match*)(d + oKf), (int32_t*)(d + oNm), nullptr);
     if (rc == ORBFE_OK && e == cudaSuccess) e = cudaDeviceSynchronize();
     if (rc == ORBFE_OK && e == cudaSuccess && n_f) e = cudaMemcpy(match_f, d + oMatch, (size_t)n_f * 4, cudaMemcpyDeviceToHost);
     if (rc == ORBFE_OK && e == cudaSuccess && kf_out && n_kf) e = cudaMemcpy(kf_out, d + oKf, (size_t)n_kf * sizeof(orbfe_match), cudaMemcpyDeviceToHost);

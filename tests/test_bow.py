@@ -195,7 +195,7 @@ def make_pair(seed, rows, n_kf, n_f, turn=25.0):
     return d_kf, k_kf, has_mp, d_f, k_f
 
 
-def python_search_by_bow(d_kf, k_kf, fv_kf, has_mp, d_f, k_f, fv_f, th_low, ratio, check_ori, kf_kf=False, has_mp_f=None):
+def python_search_by_bow(d_kf, k_kf, fv_kf, has_mp, d_f, k_f, fv_f, th_low, ratio, check_ori, kf_kf=False, has_mp_f=None, n_left_f=-1):
     """ORBmatcher::SearchByBoW(pKF, F, ...) (F.Nleft == -1) in plain Python, written from src/ORBmatcher.cc:269-470."""
     f32 = np.float32
     match = np.full(len(d_f), -1, np.int32)
@@ -206,14 +206,21 @@ def python_search_by_bow(d_kf, k_kf, fv_kf, has_mp, d_f, k_f, fv_f, th_low, rati
             if not has_mp[ikf]:
                 continue
             b1, b2, bi = 256, 256, -1
+            r1, r2, ri = 256, 256, -1                      # the right camera's rows of a fisheye rig compete separately
             for i_f in fv_f[node]:
                 if match[i_f] >= 0 or (kf_kf and has_mp_f is not None and not has_mp_f[i_f]):
                     continue
                 d = int(POPC[d_kf[ikf] ^ d_f[i_f]].sum())
-                if d < b1:
-                    b2, b1, bi = b1, d, i_f
-                elif d < b2:
-                    b2 = d
+                if n_left_f < 0 or kf_kf or i_f < n_left_f:
+                    if d < b1:
+                        b2, b1, bi = b1, d, i_f
+                    elif d < b2:
+                        b2 = d
+                else:
+                    if d < r1:
+                        r2, r1, ri = r1, d, i_f
+                    elif d < r2:
+                        r2 = d
             if (b1 < th_low if kf_kf else b1 <= th_low) and f32(b1) < f32(ratio) * f32(b2):
                 match[bi] = ikf
                 nm += 1
@@ -223,6 +230,15 @@ def python_search_by_bow(d_kf, k_kf, fv_kf, has_mp, d_f, k_f, fv_f, th_low, rati
                         rot = f32(rot + f32(360))
                     b = int(np.floor(abs(float(f32(rot * f32(f32(1) / f32(30))))) + 0.5))
                     hist[0 if b == 30 else b].append(bi)
+            if not kf_kf and n_left_f >= 0 and b1 <= th_low and r1 <= th_low:      # ORBmatcher.cc:388-416 (`|| true`)
+                match[ri] = ikf
+                nm += 1
+                if check_ori:
+                    rot = f32(k_kf["angle"][ikf]) - f32(k_f["angle"][ri])
+                    if rot < 0:
+                        rot = f32(rot + f32(360))
+                    b = int(np.floor(abs(float(f32(rot * f32(f32(1) / f32(30))))) + 0.5))
+                    hist[0 if b == 30 else b].append(ri)
     if check_ori:
         ind, mx = [-1, -1, -1], [0, 0, 0]
         for i, h in enumerate(hist):
@@ -259,6 +275,11 @@ def test_oracle_search_by_bow_matches_python():
             want, wnm = python_search_by_bow(d_kf, k_kf, fv_kf, has_mp, d_f, k_f, fv_f, 50, 0.7, ori)
             assert np.array_equal(match, want) and nm == wnm, (k, L, levelsup, ori)
             assert nm > 50 and (not ori or (kf_out["accepted"] == 2).sum() > 0)
+        # a fisheye rig: the second half of the frame's rows belongs to the right camera
+        for ori in (True, False):
+            match, kf_out, nm = O.search_by_bow(d_kf, k_kf, fv_kf, has_mp, d_f, k_f, fv_f, 50, 0.7, ori, n_left_f=n_f // 2)
+            want, wnm = python_search_by_bow(d_kf, k_kf, fv_kf, has_mp, d_f, k_f, fv_f, 50, 0.7, ori, n_left_f=n_f // 2)
+            assert np.array_equal(match, want) and nm == wnm and (match[n_f // 2:] >= 0).sum() > 10, (k, L, "fisheye", ori)
         # the keyframe-keyframe overload: candidates need a map point as well, threshold strict (49 here, so that ties at the limit occur)
         mp_f = (np.random.RandomState(seed).uniform(size=n_f) < 0.7).astype(np.uint8)
         match, kf_out, nm = O.search_by_bow(d_kf, k_kf, fv_kf, has_mp, d_f, k_f, fv_f, 20, 0.7, True, kf_kf=True, has_map_point_f=mp_f)
@@ -280,6 +301,11 @@ def test_gpu_search_by_bow_matches_oracle():
             got = B.search_by_bow(d_kf, k_kf, fv_kf, has_mp, d_f, k_f, fv_f, 50, 0.7, ori)
             assert np.array_equal(got[0], want[0]) and got[2] == want[2], (k, L, levelsup, n_kf, n_f, ori)
             assert np.array_equal(got[1], want[1]), (k, L, levelsup, n_kf, n_f, ori)
+        if n_f > 1:
+            for ori in (True, False):
+                want = O.search_by_bow(d_kf, k_kf, fv_kf, has_mp, d_f, k_f, fv_f, 50, 0.7, ori, n_left_f=n_f // 2)
+                got = B.search_by_bow(d_kf, k_kf, fv_kf, has_mp, d_f, k_f, fv_f, 50, 0.7, ori, n_left_f=n_f // 2)
+                assert np.array_equal(got[0], want[0]) and got[2] == want[2] and np.array_equal(got[1], want[1]), (k, L, n_kf, n_f, "fisheye", ori)
         mp_f = (np.random.RandomState(seed).uniform(size=n_f) < 0.7).astype(np.uint8)
         want = O.search_by_bow(d_kf, k_kf, fv_kf, has_mp, d_f, k_f, fv_f, 20, 0.7, True, kf_kf=True, has_map_point_f=mp_f)
         got = B.search_by_bow(d_kf, k_kf, fv_kf, has_mp, d_f, k_f, fv_f, 20, 0.7, True, kf_kf=True, has_map_point_f=mp_f)
@@ -313,7 +339,7 @@ def test_gpu_extract_bow_search_chain_on_device():
         d_match = torch.zeros((len(pairs_kf), ex.capacity), dtype=torch.int32, device="cuda")
         d_nm = torch.zeros(len(pairs_kf), dtype=torch.int32, device="cuda")
         _lib.check(_lib.lib().orbfe_search_by_bow_device(0, len(pairs_kf), ex.capacity, d_pk.data_ptr(), d_pf.data_ptr(), d_desc, d_kps, ex.capacity,
-                                                         bv[5].value, bv[6].value, bv[7].value, bv[8].value, None, 50, C.c_float(0.7), 1, 0,
+                                                         bv[5].value, bv[6].value, bv[7].value, bv[8].value, None, None, 50, C.c_float(0.7), 1, 0,
                                                          d_match.data_ptr(), None, d_nm.data_ptr(), st.cuda_stream))
         match, nm = d_match.cpu().numpy(), d_nm.cpu().numpy()
     st.synchronize()
