@@ -178,7 +178,7 @@ static int launch_top2(const uint8_t* dQ, int nq, const uint8_t* dDb, long long 
 }
 
 /* --------------------------------------------------------------------------------------------------- stereo */
-#define ST_NT 256
+#define ST_NT 64
 #define ST_BANDSHIFT 3
 /* One CTA = one frame: bucket the right keypoints by the 8-row band of their y (counting sort in shared memory), so that
  * the matcher only walks the bands that can hold candidates for a left keypoint's row instead of every right keypoint.
@@ -211,7 +211,7 @@ __global__ void __launch_bounds__(256) k_stereo_bucket(const __grid_constant__ E
     }
 }
 
-#define ST_KPB 8   /* left keypoints per CTA = warps per CTA */
+#define ST_KPB 2   /* left keypoints per CTA = warps per CTA */
 /* One warp = one left keypoint.  Lanes stride over the right keypoints of the bands whose rows can reach this keypoint's
  * row (a right keypoint covers rows [floor(y-r), ceil(y+r)] with r <= 2*maxScale), apply the reference's gates (row band,
  * octave +-1, disparity range), keep (distance, original index) minima — the reference scans in index order with a
