@@ -706,7 +706,7 @@ __global__ void __launch_bounds__(FS_WARPS * 32, 8) k_fast_stream(const __grid_c
  * keep the strict local maxima (cv::FAST nonmaxSuppression: neighbours outside the cell's candidate area or below the
  * threshold count as 0), write them in (y, x) order.  A cell that ends up empty is queued for the minTh fallback
  * (k_fast_cells_list). */
-#define FN_WARPS 4
+#define FN_WARPS 1
 #define FN_TP 72
 __global__ void __launch_bounds__(FN_WARPS * 32) k_fast_nms(const __grid_constant__ ExDesc d, ExBuffers b) {
     __shared__ __align__(16) uint8_t s_scAll[FN_WARPS][FN_TP * 80];   /* (ch+2) rows x tp <= 72 x 80 */
