@@ -56,6 +56,7 @@ __global__ void __launch_bounds__(256) k_pyramid_copy0(const __grid_constant__ E
  * (c0*S[sx] + c1*S[sx+1], 16-bit coefficients x 8-bit pixels); groups that touch the border recompute the reflected
  * interior pixel byte-wise.  Arithmetic is OpenCV's 11-bit fixed point. */
 
+#define PYR_WARPS 2   /* warps per CTA (they are independent: small CTAs free their slots sooner) */
 #define PYR_ROWS 4   /* output rows per thread: the horizontal tables, selectors and shifts are shared between them */
 /* Geometry of one resize launch, passed by value so that every field sits at a fixed constant-bank address. */
 struct ResizeArgs {
@@ -71,10 +72,10 @@ static __device__ __forceinline__ uint32_t resize_vblend(uint32_t h0, uint32_t h
 }
 
 __global__ void __launch_bounds__(256) k_pyramid_level(const __grid_constant__ ExDesc d, ExBuffers b, const __grid_constant__ ResizeArgs a) {
-    /* block = 32 x 8: a warp works on PYR_ROWS consecutive interior rows; a thread on one group of four pixels that
+    /* block = 32 x PYR_WARPS: a warp works on PYR_ROWS consecutive interior rows; a thread on one group of four pixels that
      * lies fully inside the image.  The border pixels the extractor reads (and the last 1-3 columns when w % 4 != 0) are filled
      * afterwards for all levels at once by k_pyramid_fringe: the next level's resize never reads a border pixel with a non-zero weight. */
-    const int row0 = (blockIdx.y * 8 + threadIdx.y) * PYR_ROWS;   /* interior row */
+    const int row0 = (blockIdx.y * PYR_WARPS + threadIdx.y) * PYR_ROWS;   /* interior row */
     if (row0 >= a.h) return;
     const int tx = blockIdx.x * 32 + threadIdx.x;
     if (tx >= ((a.w + 3) >> 2)) return;   /* a partial last group (w % 4 != 0) is computed like a full one, see the x table */
@@ -1318,7 +1319,7 @@ int orbfe_launch_extract(orbfe_extractor* ex, const uint8_t* d_images, int nfram
     }
     for (int l = 1; l < d.nlevels; l++) {
         const LevelDesc& L = d.lv[l];
-        k_pyramid_level<<<dim3(((L.w + 3) / 4 + 31) / 32, (L.h + 8 * PYR_ROWS - 1) / (8 * PYR_ROWS), nframes), dim3(32, 8), 0, st>>>(
+        k_pyramid_level<<<dim3(((L.w + 3) / 4 + 31) / 32, (L.h + PYR_WARPS * PYR_ROWS - 1) / (PYR_WARPS * PYR_ROWS), nframes), dim3(32, PYR_WARPS), 0, st>>>(
             d, xb, ResizeArgs{L.w, L.h, L.pitch, L.pyrOff, d.lv[l - 1].pitch, d.lv[l - 1].pyrOff, L.tabX, L.tabY});
     }
     {
