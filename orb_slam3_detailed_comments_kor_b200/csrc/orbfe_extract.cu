@@ -578,7 +578,7 @@ __global__ void __launch_bounds__(FAST_NT, 8) k_fast_cells_list(const __grid_con
 #define FS_R 8          /* rows per compaction chunk */
 #define FS_COLS 120     /* candidate columns per strip (lanes 1..30; lanes 0 and 31 carry the 4 px halos) */
 
-/* One warp = one strip (120 columns x up to 48 rows) of one level of one frame; warps are independent (no block
+/* One warp = one strip (120 columns x up to 32 rows; one strip = one CTA) of one level of one frame; warps are independent (no block
  * barrier).  Each lane owns four adjacent columns.  Per row the warp loads the row three below (coalesced 128 B),
  * keeps the last 16 rows in a shared-memory ring, and runs the 4-pixel sieve on registers (left/right neighbours come
  * by shuffle).  Every FS_R rows the sieve's survivors are compacted (per-lane bit masks, one warp scan) into a queue,

@@ -50,7 +50,7 @@ struct ExDesc {
     int iniTh, minTh;
     int blurTile0[ORBFE_MAX_LEVELS + 1]; /* first blur tile of each level in the one blur launch; [nlevels] = total */
     int stBands;      /* 8-row bands of the stereo candidate table: (H >> 3) + 1 */
-    int nStrips;      /* strips of k_fast_stream per frame (48-row cut) */
+    int nStrips;      /* strips of k_fast_stream per frame (32-row cut) */
     int nStripsShort; /* 16-row cut, stored after the first in b.strips; used for launches of a few frames */
     int rawCap;       /* raw-corner slots per frame */
     int fastRows;     /* tallest FAST cell ROI (rows of the smem tile) */
