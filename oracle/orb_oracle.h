@@ -9,12 +9,20 @@
  * `find_package(OpenCV 4.0)`; the arithmetic restated here is pinned against cv2 4.13.0 by
  * tools/make_goldens.py -> tests/golden/, see tests/test_oracle_golden.py).
  *
+ * Parity is PINNED twice: the OpenCV primitives against the real cv2 4.13 (above), and the extractor and
+ * the stereo matcher as a whole against the reference's own ORBextractor.cc / Frame::ComputeStereoMatches
+ * compiled in this container (oracle/Makefile -> oracle/_ref/liborb_ref.so, tests/test_ref_pinned.py):
+ * identical keypoints, angles, descriptors, pyramids, uRight and depth on every golden case.
+ *
  * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may
  * load this library.  The product (liborbfe.so) never links, imports or calls it.
  *
  * Defined deviations from the reference:
- *  (i)   quadtree equal-size tie-break = node creation order (the reference sorts by heap address);
- *  (ii)  stereo maxD is an explicit argument (the reference reads an uninitialised `mb`);
+ *  (i)   quadtree equal-size tie-break = node creation order (the reference sorts by heap address, which is
+ *        creation order under a monotonic allocator -- the one oracle/_ref is run with -- and differs under
+ *        glibc malloc, where the reference's own output changes with the state of the heap);
+ *  (ii)  stereo maxD is an explicit argument (the reference computes mbf/mb, src/Frame.cc:827-829, with mb = mbf/fx
+ *        from the Frame constructor, :173; callers pass that float, which is fx up to one rounding);
  *  (iii) empty stereo match list => no median cut (the reference indexes an empty vector);
  *  (iv)  float arithmetic is IEEE binary32 without FMA contraction (-ffp-contract=off).
  */

@@ -1,0 +1,133 @@
+"""ctypes loader for oracle/_ref/liborb_ref.so: the REFERENCE'S OWN ORBextractor.cc (compiled unmodified) and the bodies of
+Frame::ComputeStereoMatches / ORBmatcher::DescriptorDistance, built by oracle/Makefile.  TEST INFRASTRUCTURE ONLY.
+
+The library can only be built where /root/reference exists (this container); the GPU box receives the prebuilt file.
+Only tests/ and bench.py's cpu_baseline / --impl reference legs import this module.  See oracle/ref_shim.cpp.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+from .orb_oracle import KP_DTYPE
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+REF_SRC = os.environ.get("ORBFE_REFERENCE", "/root/reference")
+_libs = {}
+
+
+def so_path(fma=False):
+    return os.path.join(_HERE, "_ref", "liborb_ref_fma.so" if fma else "liborb_ref.so")
+
+
+def build():
+    """Run the committed recipe (oracle/Makefile) when the reference sources are present; otherwise keep what is there."""
+    if os.path.exists(os.path.join(REF_SRC, "src", "ORBextractor.cc")):
+        subprocess.check_call(["make", "-C", _HERE, "REF=" + REF_SRC, "_ref/liborb_ref.so", "_ref/liborb_ref_fma.so"], stdout=subprocess.DEVNULL)
+    return so_path() if os.path.exists(so_path()) else None
+
+
+def available(fma=False):
+    return os.path.exists(so_path(fma)) or build() is not None
+
+
+def lib(fma=False):
+    if fma in _libs:
+        return _libs[fma]
+    if not available(fma):
+        raise RuntimeError("oracle/_ref is not built and %s is absent" % REF_SRC)
+    L = C.CDLL(so_path(fma))
+    vp, i32p = C.c_void_p, C.POINTER(C.c_int32)
+    par = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int]
+    L.ref_set_arena.argtypes = [C.c_int]
+    L.ref_arena_peak.restype = C.c_size_t
+    L.ref_tables.argtypes = par + [vp, vp, vp]
+    L.ref_extract.argtypes = par + [vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp, vp, C.c_int, i32p, vp]
+    L.ref_level_keypoints.argtypes = par + [vp, C.c_int, C.c_int, C.c_int, vp, C.c_int, vp]
+    L.ref_stereo.argtypes = par + [vp, vp, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, vp, vp, i32p, vp, vp, i32p, C.c_int, vp, vp]
+    L.ref_descriptor_distance.argtypes = [vp, vp]
+    _libs[fma] = L
+    return L
+
+
+def _ptr(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+class ReferenceExtractor:
+    """ORB_SLAM3::ORBextractor itself (include/ORBextractor.h:43-109); a fresh C++ object per call, as the tables are cheap."""
+
+    def __init__(self, nfeatures=1200, scale_factor=1.2, nlevels=8, ini_th=20, min_th=7, fma=False):
+        self.L = lib(fma)
+        self.params = (int(nfeatures), float(scale_factor), int(nlevels), int(ini_th), int(min_th))
+        self.nfeatures, self.nlevels = int(nfeatures), int(nlevels)
+
+    def tables(self):
+        q, u, s = np.zeros(self.nlevels, np.int32), np.zeros(16, np.int32), np.zeros(self.nlevels, np.float32)
+        self.L.ref_tables(*self.params, _ptr(q), _ptr(u), _ptr(s))
+        return list(q), list(u), s
+
+    def level_sizes(self, width, height):
+        """cvRound((float)cols*scale) per level, src/ORBextractor.cc:1156-1157 (needed to slice the pyramid dump)."""
+        _, _, s = self.tables()
+        inv = (np.float32(1.0) / s).astype(np.float32)
+        r = lambda v: int(np.rint(np.float32(v)))  # noqa: E731
+        return [(r(np.float32(width) * inv[l]), r(np.float32(height) * inv[l])) for l in range(self.nlevels)]
+
+    def __call__(self, image, lapping=(0, 0), want_pyramid=False):
+        img = np.ascontiguousarray(image, dtype=np.uint8)
+        cap = self.nfeatures * 2 + 64 * self.nlevels
+        kps, desc, n = np.zeros(cap, KP_DTYPE), np.zeros((cap, 32), np.uint8), C.c_int32(0)
+        rows, cols = (img.shape if img.ndim == 2 else (0, 0))
+        pyr = None
+        if want_pyramid:
+            sizes = self.level_sizes(cols, rows)
+            pyr = np.zeros(sum((w + 38) * (h + 38) for w, h in sizes), np.uint8)
+        mono = self.L.ref_extract(*self.params, _ptr(img) if img.size else None, rows, cols, cols, lapping[0], lapping[1], _ptr(kps), _ptr(desc),
+                                  cap, C.byref(n), _ptr(pyr) if pyr is not None else None)
+        if mono < 0:
+            return (mono, kps[:0], desc[:0]) + ((None,) if want_pyramid else ())
+        out = (mono, kps[:n.value].copy(), desc[:n.value].copy())
+        if want_pyramid:
+            levels, o = [], 0
+            for w, h in sizes:
+                levels.append(pyr[o:o + (w + 38) * (h + 38)].reshape(h + 38, w + 38))
+                o += (w + 38) * (h + 38)
+            out += (levels,)
+        return out
+
+    def level_keypoints(self, image):
+        """Per level: keypoints after DistributeOctTree and computeOrientation, in level coordinates."""
+        img = np.ascontiguousarray(image, dtype=np.uint8)
+        cap = self.nfeatures * 2 + 64 * self.nlevels
+        out, counts = np.zeros(cap, KP_DTYPE), np.zeros(self.nlevels, np.int32)
+        total = self.L.ref_level_keypoints(*self.params, _ptr(img), img.shape[0], img.shape[1], img.shape[1], _ptr(out), cap, _ptr(counts))
+        assert total >= 0
+        off = np.concatenate([[0], np.cumsum(counts)])
+        return [out[off[l]:off[l + 1]].copy() for l in range(self.nlevels)]
+
+    def stereo(self, left, right, mbf, mb):
+        """Both extractions + Frame::ComputeStereoMatches; returns (kpsL, descL, kpsR, descR, mvuRight, mvDepth)."""
+        a, b = np.ascontiguousarray(left, np.uint8), np.ascontiguousarray(right, np.uint8)
+        cap = self.nfeatures * 2 + 64 * self.nlevels
+        kL, dL, kR, dR = np.zeros(cap, KP_DTYPE), np.zeros((cap, 32), np.uint8), np.zeros(cap, KP_DTYPE), np.zeros((cap, 32), np.uint8)
+        nL, nR, u, d = C.c_int32(0), C.c_int32(0), np.zeros(cap, np.float32), np.zeros(cap, np.float32)
+        rc = self.L.ref_stereo(*self.params, _ptr(a), _ptr(b), a.shape[0], a.shape[1], a.shape[1], mbf, mb, _ptr(kL), _ptr(dL), C.byref(nL),
+                               _ptr(kR), _ptr(dR), C.byref(nR), cap, _ptr(u), _ptr(d))
+        assert rc >= 0
+        return kL[:nL.value].copy(), dL[:nL.value].copy(), kR[:nR.value].copy(), dR[:nR.value].copy(), u[:nL.value].copy(), d[:nL.value].copy()
+
+
+def descriptor_distance(a, b, fma=False):
+    a, b = np.ascontiguousarray(a, np.uint8), np.ascontiguousarray(b, np.uint8)
+    return lib(fma).ref_descriptor_distance(_ptr(a), _ptr(b))
+
+
+def set_arena(on, fma=False):
+    """on=False: plain malloc/free instead of the monotonic arena (to see what heap-address ties do)."""
+    lib(fma).ref_set_arena(int(bool(on)))
+
+
+def arena_peak(fma=False):
+    return lib(fma).ref_arena_peak()

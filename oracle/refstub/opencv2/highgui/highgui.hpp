@@ -1,0 +1,2 @@
+/* Forwarding header: the reference includes <opencv2/highgui/highgui.hpp>; everything it uses is in cvstub.hpp (test infrastructure). */
+#include "../../cvstub.hpp"

@@ -143,6 +143,40 @@ def test_regular_patterns_stress_ties(pattern):
     ex.close()
 
 
+@pytest.mark.parametrize("name,stereo", [("euroc", (47.90639, 435.2047)), ("kitti", (386.1448, 718.856)), ("tumvi", None), ("init5x", None)])
+def test_gpu_equals_compiled_reference(name, stereo):
+    """CUDA output against the reference's own ORBextractor.cc / Frame::ComputeStereoMatches body compiled by oracle/Makefile
+    (oracle/_ref/liborb_ref.so, prebuilt where /root/reference exists; see tests/test_ref_pinned.py): keypoints, descriptors,
+    monoIndex, padded pyramid, uRight and depth bit-exact; angles within 1e-3 degrees."""
+    from oracle import ref_oracle as Rf
+    if not Rf.available():
+        pytest.skip("oracle/_ref not shipped to this machine")
+    W, H, seed, params, laps = SHAPES[name]
+    L, R = synth.stereo_pair(seed, W, H)
+    exL, exR = ORBextractor(*params, width=W, height=H), ORBextractor(*params, width=W, height=H)
+    ref = Rf.ReferenceExtractor(*params)
+    for lap in laps:
+        mono, kps, desc = exL(L, lap)
+        rmono, rkps, rdesc, pyr = ref(L, lap, want_pyramid=True)
+        assert mono == rmono
+        assert_same_keypoints(kps, rkps, "%s lap %s" % (name, lap))
+        assert np.array_equal(desc, rdesc)
+    for l in range(params[2]):
+        assert np.array_equal(exL.pyramid_level(l, padded=True), pyr[l]), "padded pyramid level %d" % l
+    if stereo:
+        mbf, fx = stereo
+        mb = np.float32(mbf) / np.float32(fx)              # Frame constructor, src/Frame.cc:173; maxD = mbf/mb, :827-829
+        kL, dL, kR, dR, u, d = ref.stereo(L, R, mbf, float(mb))
+        _, gkL, gdL = exL(L, (0, 0))
+        _, gkR, gdR = exR(R, (0, 0))
+        M.compute_stereo_matches(exL, exR, 1, mbf, 0.0, float(np.float32(mbf) / mb))
+        gu, gd = M.stereo_result(exL, 0)
+        assert_same_keypoints(gkR, kR, "right")
+        assert np.array_equal(gdL, dL) and np.array_equal(gdR, dR)
+        assert np.array_equal(gu, u) and np.array_equal(gd, d) and int((u >= 0).sum()) > 50
+    exL.close(); exR.close()
+
+
 def test_batch_paths_agree_with_oracle():
     import torch
     W, H, params, nb = 752, 480, (1200, 1.2, 8, 20, 7), 6

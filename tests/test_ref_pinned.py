@@ -1,0 +1,170 @@
+"""CPU tests: the oracle (oracle/liborb_oracle.so) against the REFERENCE'S OWN CODE compiled here (oracle/_ref/liborb_ref.so).
+
+oracle/Makefile compiles /root/reference/src/ORBextractor.cc unmodified, and the bodies of Frame::ComputeStereoMatches
+(src/Frame.cc:797-967) and ORBmatcher::DescriptorDistance (src/ORBmatcher.cc:2591-2607), against oracle/refstub/ — a small
+cv:: surface whose pixel primitives are the cv2-4.13-pinned ones (tests/test_oracle_golden.py).  So these tests pin what the
+goldens could not: the reference's glue (cell loop, DistributeOctTree and its tie order, lapping partition, IC_Angle sums,
+rotated-BRIEF tap arithmetic as g++ compiles it, stereo row search, parabola, median cut) — bit-exactly, angles included.
+
+Tolerances: none (everything is compared with array_equal), except the `_fma` build (GCC's default -ffp-contract=fast, what
+the reference's own flags produce on an FMA host), where angles may move by <= 1e-3 degrees and descriptor bits are counted.
+"""
+import os
+
+import numpy as np
+import pytest
+
+from oracle import orb_oracle as O
+from oracle import ref_oracle as Rf
+from orb_slam3_detailed_comments_kor_b200 import synth
+
+pytestmark = pytest.mark.skipif(not Rf.available(), reason="oracle/_ref not built and /root/reference absent")
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+CASES = ["euroc", "tumvi", "kitti", "small", "noise", "lowc"]
+FIELDS = ("x", "y", "size", "angle", "response", "octave", "class_id")
+
+
+def load_case(name):
+    g = np.load(os.path.join(GOLD, name + ".npz"))
+    W, H = [int(v) for v in g["wh"]]
+    L, R = (g["imgL"], g["imgR"]) if "imgL" in g else synth.stereo_pair(int(g["seed"][0]), W, H)
+    p = g["params"]
+    laps, li = [], 0
+    while "lap%d" % li in g:
+        laps.append(tuple(int(v) for v in g["lap%d" % li]))
+        li += 1
+    return L, R, (int(p[0]), float(p[1]), int(p[2]), int(p[3]), int(p[4])), laps
+
+
+def patterns():
+    H, W = 480, 640
+    yy, xx = np.mgrid[0:H, 0:W]
+    rng = np.random.RandomState(5)
+    return {
+        "dots": np.where(((xx % 12) < 3) & ((yy % 12) < 3), 220, 40).astype(np.uint8),
+        "checker": np.where(((xx // 16) + (yy // 16)) % 2 == 0, 200, 60).astype(np.uint8),
+        "stripes_noise": (np.where((xx // 9) % 2 == 0, 180, 70) + rng.randint(-12, 13, (H, W))).clip(0, 255).astype(np.uint8),
+    }
+
+
+def assert_identical(got, want, what):
+    assert len(got) == len(want), "%s: %d vs %d keypoints" % (what, len(got), len(want))
+    for f in FIELDS:
+        assert np.array_equal(got[f], want[f]), "%s: field %s differs" % (what, f)
+
+
+def check_image(img, params, laps, stages=True):
+    orc, ref = O.OracleExtractor(*params), Rf.ReferenceExtractor(*params)
+    for lap in laps:
+        mono, kps, desc = orc(img, lap)
+        rmono, rkps, rdesc, pyr = ref(img, lap, want_pyramid=True)
+        assert mono == rmono
+        assert_identical(kps, rkps, "lap %s" % (lap,))
+        assert np.array_equal(desc, rdesc)
+    if stages:
+        for l in range(params[2]):
+            assert np.array_equal(orc.pyramid_level(l, padded=True), pyr[l]), "padded pyramid level %d" % l
+        for l, rk in enumerate(ref.level_keypoints(img)):
+            assert_identical(orc.level_keypoints(l), rk, "level %d after quadtree + orientation" % l)
+    return len(kps)
+
+
+@pytest.mark.parametrize("params", [(1200, 1.2, 8, 20, 7), (1000, 1.2, 8, 20, 7), (1500, 1.2, 8, 20, 7), (2000, 1.2, 8, 20, 7),
+                                    (5000, 1.2, 8, 20, 7), (500, 1.5, 4, 30, 10), (300, 2.0, 3, 20, 7)])
+def test_constructor_tables(params):
+    """E0, src/ORBextractor.cc:408-468: quotas, umax, scale factors."""
+    q, u, s = Rf.ReferenceExtractor(*params).tables()
+    orc = O.OracleExtractor(*params)
+    assert orc.quotas() == q and orc.umax() == u
+    assert np.array_equal(np.array(orc.scale_factors(), np.float32), s)
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_extractor_equals_reference_on_golden_cases(name):
+    L, R, params, laps = load_case(name)
+    assert check_image(L, params, laps) > 0
+    check_image(R, params, laps[:1])
+
+
+@pytest.mark.parametrize("pattern", ["dots", "checker", "stripes_noise"])
+def test_extractor_equals_reference_on_tie_patterns(pattern):
+    """Equal FAST scores and many equal-sized quadtree nodes: the order sort() gives pair<size, node address>
+    (src/ORBextractor.cc:682) decides which nodes split.  With addresses that grow with creation it is the oracle's rule."""
+    assert check_image(patterns()[pattern], (1000, 1.2, 8, 20, 7), [(0, 0), (0, 1000)]) > 300
+
+
+def test_extractor_equals_reference_more_shapes():
+    for seed, (W, H, params) in enumerate([(1241, 376, (10000, 1.2, 8, 20, 7)), (320, 240, (500, 1.2, 8, 20, 7)), (1980, 1270, (5000, 1.2, 8, 20, 7)),
+                                           (641, 479, (1000, 1.2, 8, 20, 7)), (400, 400, (800, 1.5, 4, 30, 10))]):
+        check_image(synth.frame(40 + seed, W, H), params, [(0, 0), (W // 4, W // 2)], stages=False)
+    mono, kps, _ = Rf.ReferenceExtractor()(np.zeros((0, 0), np.uint8))
+    assert mono == -1 and len(kps) == 0                                   # src/ORBextractor.cc:1072-1073
+    flat = np.full((480, 752), 128, np.uint8)
+    assert check_image(flat, (1200, 1.2, 8, 20, 7), [(0, 0)]) == 0
+
+
+def test_reference_ties_depend_on_the_allocator():
+    """Documents deviation (i): with glibc malloc instead of the monotonic arena the reference itself returns a different
+    keypoint set on a tie-heavy image (node addresses no longer follow creation), so no fixed rule can equal it on every
+    heap.  The arena run equals the oracle (tests above)."""
+    img = patterns()["dots"]
+    ref = Rf.ReferenceExtractor(1000, 1.2, 8, 20, 7)
+    _, a, _ = ref(img)
+    assert Rf.arena_peak() > 0                                            # the arena really served the reference's `new`
+    Rf.set_arena(False)
+    try:
+        _, b, _ = ref(img)
+    finally:
+        Rf.set_arena(True)
+    _, c, _ = ref(img)
+    assert_identical(a, c, "arena runs repeat")
+    assert len(a) != len(b) or not np.array_equal(a["x"], b["x"]) or not np.array_equal(a["y"], b["y"])
+
+
+@pytest.mark.parametrize("name,mbf,fx", [("euroc", 47.90639, 435.2047), ("kitti", 386.1448, 718.856), ("lowc", 47.90639, 435.2047)])
+def test_stereo_equals_reference(name, mbf, fx):
+    """Frame::ComputeStereoMatches (src/Frame.cc:797-967).  The reference computes maxD = mbf/mb (:827-829) with mb = mbf/fx
+    set by the Frame constructor (src/Frame.cc:173); the oracle takes maxD as an argument and gets that same float."""
+    L, R, params, _ = load_case(name)
+    mb = np.float32(mbf) / np.float32(fx)
+    max_d = float(np.float32(mbf) / mb)
+    kL, dL, kR, dR, u, d = Rf.ReferenceExtractor(*params).stereo(L, R, mbf, float(mb))
+    oL, oR = O.OracleExtractor(*params), O.OracleExtractor(*params)
+    _, okL, odL = oL(L)
+    _, okR, odR = oR(R)
+    assert_identical(okL, kL, "left")
+    assert_identical(okR, kR, "right")
+    kept, ou, od = O.stereo_match(oL, oR, okL, odL, okR, odR, mbf, 0.0, max_d)
+    assert np.array_equal(u, ou) and np.array_equal(d, od)
+    assert kept == int((u >= 0).sum()) and kept > 20
+
+
+def test_descriptor_distance_equals_reference():
+    rng = np.random.RandomState(3)
+    z, o = np.zeros(32, np.uint8), np.full(32, 255, np.uint8)
+    one = z.copy(); one[17] = 0x10
+    assert [Rf.descriptor_distance(z, z), Rf.descriptor_distance(z, o), Rf.descriptor_distance(z, one)] == [0, 256, 1]
+    for _ in range(500):
+        a, b = rng.randint(0, 256, 32).astype(np.uint8), rng.randint(0, 256, 32).astype(np.uint8)
+        assert Rf.descriptor_distance(a, b) == O.descriptor_distance(a, b) == int(np.unpackbits(a ^ b).sum())
+    L = Rf.lib()
+    assert (L.ref_th_low(), L.ref_th_high()) == (50, 100)                  # src/ORBmatcher.cc:36-37
+
+
+def test_fma_contracted_reference_build_stays_within_tolerance():
+    """The reference's CMake flags (-O3 -march=native, GNU C++ default -ffp-contract=fast) let g++ fuse multiply-adds on an FMA
+    host.  Same sources built that way: keypoints identical, angles within the 1e-3 degree tolerance, and the descriptor
+    bits that move are counted (the parity statement is for the uncontracted evaluation; this bounds the other one)."""
+    moved = total = 0
+    for seed in range(6):
+        img = synth.frame(seed, 752, 480)
+        _, k, d = Rf.ReferenceExtractor()(img)
+        _, kf, df = Rf.ReferenceExtractor(fma=True)(img)
+        assert len(k) == len(kf)
+        for f in ("x", "y", "size", "response", "octave"):
+            assert np.array_equal(k[f], kf[f])
+        assert np.max(np.abs(k["angle"] - kf["angle"])) <= 1e-3
+        moved += int(np.unpackbits(d ^ df).sum())
+        total += d.size * 8
+    assert moved <= total * 1e-4, "%d of %d descriptor bits moved" % (moved, total)
