@@ -211,7 +211,9 @@ void orbfe_vocabulary_destroy(orbfe_vocabulary* v);
 int orbfe_vocabulary_words(const orbfe_vocabulary* v);
 /* A batch of frames on the device: frame f owns d_counts[f] descriptors at d_desc + (f*row_stride + i)*32 — the layout of
  * orbfe_batch_device_views (row_stride = keypoint capacity), so the extractor's buffers can be passed as they are.
- * Asynchronous on `stream` (NULL = the object's stream); results stay in the object until the next call. */
+ * Asynchronous on `stream` (NULL = the object's stream); results stay in the object until the next call.
+ * A frame with d_counts[f] > max_features (the extractor's capacity can exceed 4096 for large nfeatures) is not silently
+ * truncated: its bow / feature-vector counts are set to -1 on the device and orbfe_bow_result returns ORBFE_E_CAPACITY for it. */
 int orbfe_bow_transform_batch_device(orbfe_vocabulary* v, const uint8_t* d_desc, int row_stride, const int32_t* d_counts, int nframes,
                                      int levelsup, void* stream);
 /* Results of frame `frame` of the last batch, to the host (any pointer may be NULL):

@@ -188,6 +188,8 @@ __global__ void __launch_bounds__(BOW_NT) k_bow_assemble(const int* __restrict__
         if (e >= 0) { fvNodes[fo + e] = (int)(unsigned)(key[j] >> 32); fvStarts[so + e] = j; }
     }
     if (tid == 0) { fvStarts[so + nn] = nv; fvCount[f] = nn; }
+    /* more descriptors than the object holds: DBoW2 would use them all, so the truncated vectors are marked unusable */
+    if (tid == 0 && counts[f] > maxF) { bowCount[f] = -1; fvCount[f] = -1; }
 }
 
 /* ------------------------------------------------------------------------------------------------- SearchByBoW */
@@ -588,6 +590,10 @@ int orbfe_bow_result(orbfe_vocabulary* v, int frame, int nfeatures, int32_t* wor
     int nb = 0, nn = 0;
     ORBFE_CUDA(cudaMemcpy(&nb, v->bowCount + frame, 4, cudaMemcpyDeviceToHost));
     ORBFE_CUDA(cudaMemcpy(&nn, v->fvCount + frame, 4, cudaMemcpyDeviceToHost));
+    if (nb < 0 || nn < 0) {
+        orbfe_set_error("frame %d of the batch has more than max_features = %d descriptors: its BoW vectors were not computed", frame, v->maxFeatures);
+        return ORBFE_E_CAPACITY;
+    }
     if (nbow) *nbow = nb;
     if (nfv) *nfv = nn;
     if (word_ids && nfeatures) ORBFE_CUDA(cudaMemcpy(word_ids, v->featWord + fo, (size_t)nfeatures * 4, cudaMemcpyDeviceToHost));

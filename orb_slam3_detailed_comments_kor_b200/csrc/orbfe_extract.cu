@@ -16,6 +16,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <mutex>
+
 #include "orbfe_internal.h"
 #include "orbfe_trig.cuh"
 
@@ -791,6 +793,7 @@ __global__ void __launch_bounds__(FN_WARPS * 32) k_fast_nms(const __grid_constan
 
 /* ----------------------------------------------------------------------------------------------- quadtree */
 #define QT_NT 256
+#define QT_NOKEY 0xFFFFFFFFFFFFFFFFull   /* sorts behind every real key */
 
 /* In-place exclusive scan of data[0..n) by the whole CTA; returns the total. tmp: QT_NT/32+1 ints. */
 static __device__ int block_exscan(int* data, int n, int* tmp) {
@@ -865,7 +868,7 @@ __global__ void __launch_bounds__(QT_NT) k_quadtree(const __grid_constant__ ExDe
     int* childCnt = cnt1 + cap;            /* [cap][4] */
     int* scanA = childCnt + 4 * cap;       /* [cap] S: children before me in processing order */
     int* scanB = scanA + cap;              /* [cap] unexpanded-before-me */
-    uint32_t* sortK = reinterpret_cast<uint32_t*>(scanB + cap); /* [cap] */
+    uint64_t* sortK = reinterpret_cast<uint64_t*>(scanB + cap); /* [cap] (~size << 32 | list position): any node count, any node size */
     uint16_t* childPos = reinterpret_cast<uint16_t*>(sortK + cap); /* [cap][4] */
     uint16_t* newPos = childPos + 4 * cap; /* [cap] */
     uint8_t* expand = reinterpret_cast<uint8_t*>(newPos + cap); /* [cap] */
@@ -974,14 +977,14 @@ __global__ void __launch_bounds__(QT_NT) k_quadtree(const __grid_constant__ ExDe
             int n2 = 1;
             while (n2 < nNew) n2 <<= 1;
             for (int i = tid; i < n2; i += QT_NT)
-                sortK[i] = (i < nNew && expand[i]) ? (((uint32_t)(524287 - min(cnt[i], 524287)) << 13) | (uint32_t)i) : 0xFFFFFFFFu;
+                sortK[i] = (i < nNew && expand[i]) ? (((uint64_t)(~(uint32_t)cnt[i]) << 32) | (uint32_t)i) : QT_NOKEY;
             __syncthreads();
             for (int k2 = 2; k2 <= n2; k2 <<= 1)
                 for (int j = k2 >> 1; j > 0; j >>= 1) {
                     for (int i = tid; i < n2; i += QT_NT) {
                         const int ixj = i ^ j;
                         if (ixj > i) {
-                            const uint32_t a = sortK[i], c = sortK[ixj];
+                            const uint64_t a = sortK[i], c = sortK[ixj];
                             const bool up = (i & k2) == 0;
                             if ((a > c) == up) { sortK[i] = c; sortK[ixj] = a; }
                         }
@@ -991,8 +994,8 @@ __global__ void __launch_bounds__(QT_NT) k_quadtree(const __grid_constant__ ExDe
             /* scanB[j] = list growth when the j-th candidate is divided (children - 1) */
             for (int j = tid; j < nNew; j += QT_NT) {
                 int g = 0;
-                if (sortK[j] != 0xFFFFFFFFu) {
-                    const int i = sortK[j] & 0x1FFF;
+                if (sortK[j] != QT_NOKEY) {
+                    const int i = (int)(uint32_t)sortK[j];
                     g = (childCnt[4 * i] > 0) + (childCnt[4 * i + 1] > 0) + (childCnt[4 * i + 2] > 0) + (childCnt[4 * i + 3] > 0) - 1;
                 }
                 scanB[j] = g;
@@ -1002,8 +1005,8 @@ __global__ void __launch_bounds__(QT_NT) k_quadtree(const __grid_constant__ ExDe
             block_exscan(scanB, nNew, s_tmp);
             /* first j whose inclusive growth brings the list to N: everything after it is left alone */
             for (int j = tid; j < nNew; j += QT_NT) {
-                if (sortK[j] == 0xFFFFFFFFu) continue;
-                const int i = sortK[j] & 0x1FFF;
+                if (sortK[j] == QT_NOKEY) continue;
+                const int i = (int)(uint32_t)sortK[j];
                 const int g = (childCnt[4 * i] > 0) + (childCnt[4 * i + 1] > 0) + (childCnt[4 * i + 2] > 0) + (childCnt[4 * i + 3] > 0) - 1;
                 if (prevSize + scanB[j] + g >= N) atomicMin(&s_cut, j);
             }
@@ -1014,8 +1017,8 @@ __global__ void __launch_bounds__(QT_NT) k_quadtree(const __grid_constant__ ExDe
             /* children of the candidates that do get divided, prefixed in processing (= sorted) order */
             for (int j = tid; j < nNew; j += QT_NT) {
                 int nch = 0;
-                if (sortK[j] != 0xFFFFFFFFu && j <= cut) {
-                    const int i = sortK[j] & 0x1FFF;
+                if (sortK[j] != QT_NOKEY && j <= cut) {
+                    const int i = (int)(uint32_t)sortK[j];
                     expand[i] = 1;
                     nch = (childCnt[4 * i] > 0) + (childCnt[4 * i + 1] > 0) + (childCnt[4 * i + 2] > 0) + (childCnt[4 * i + 3] > 0);
                 }
@@ -1024,7 +1027,7 @@ __global__ void __launch_bounds__(QT_NT) k_quadtree(const __grid_constant__ ExDe
             __syncthreads();
             C = block_exscan(scanB, nNew, s_tmp);
             for (int j = tid; j < nNew; j += QT_NT)
-                if (sortK[j] != 0xFFFFFFFFu && j <= cut) scanA[sortK[j] & 0x1FFF] = scanB[j];
+                if (sortK[j] != QT_NOKEY && j <= cut) scanA[(uint32_t)sortK[j]] = scanB[j];
             __syncthreads();
         }
         if (!partial) C = block_exscan(scanA, nCur, s_tmp);
@@ -1273,17 +1276,32 @@ int orbfe_upload_constants(const int* umax16, const int8_t* pattern1024) {
 }
 
 int orbfe_quadtree_smem_bytes(int cap) {
-    /* box 2x8 + cnt 2x4 + childCnt 16 + scanA 4 + scanB 4 + sortK 4 + childPos 8 + newPos 2 + expand 1 */
-    return cap * (16 + 8 + 16 + 4 + 4 + 4 + 8 + 2 + 1) + 64;
+    /* box 2x8 + cnt 2x4 + childCnt 16 + scanA 4 + scanB 4 + sortK 8 + childPos 8 + newPos 2 + expand 1 */
+    return cap * (16 + 8 + 16 + 4 + 4 + 8 + 8 + 2 + 1) + 64;
 }
 
 int orbfe_collect_stage_times(orbfe_extractor* ex);
 
 int orbfe_blur_tiles(int w, int h) { return ((w + BLUR_TW - 1) / BLUR_TW) * ((h + BLUR_TH - 1) / BLUR_TH); }
 
+/* The dynamic shared-memory limit is a property of the kernel on a device, not of an extractor object: extractors of
+ * different sizes live side by side (Tracking holds mpIniORBextractor with 5 x nFeatures next to the per-frame one,
+ * /root/reference/src/Tracking.cc:1151-1157), so the limit only ever grows to the largest request seen on the device. */
 int orbfe_configure_kernels(int quadSmem, int fastSmem) {
-    ORBFE_CUDA(cudaFuncSetAttribute(k_quadtree<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, quadSmem));
-    ORBFE_CUDA(cudaFuncSetAttribute(k_fast_cells_list, cudaFuncAttributeMaxDynamicSharedMemorySize, fastSmem));
+    static std::mutex mu;
+    static int quadMax[ORBFE_MAX_DEVICES], fastMax[ORBFE_MAX_DEVICES];
+    int dev = 0;
+    ORBFE_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= ORBFE_MAX_DEVICES) { orbfe_set_error("device ordinal %d out of range", dev); return ORBFE_E_INVALID; }
+    std::lock_guard<std::mutex> lock(mu);
+    if (quadSmem > quadMax[dev]) {
+        ORBFE_CUDA(cudaFuncSetAttribute(k_quadtree<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, quadSmem));
+        quadMax[dev] = quadSmem;
+    }
+    if (fastSmem > fastMax[dev]) {
+        ORBFE_CUDA(cudaFuncSetAttribute(k_fast_cells_list, cudaFuncAttributeMaxDynamicSharedMemorySize, fastSmem));
+        fastMax[dev] = fastSmem;
+    }
     return 0;
 }
 

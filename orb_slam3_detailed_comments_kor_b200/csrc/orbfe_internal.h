@@ -9,6 +9,7 @@
 #include "../../include/orbfe.h"
 
 #define ORBFE_MAX_LEVELS 16
+#define ORBFE_MAX_DEVICES 64  /* per-device bookkeeping tables (kernel attributes, static scratch addresses) */
 #define ORBFE_EDGE 19        /* EDGE_THRESHOLD, src/ORBextractor.cc:72 */
 #define ORBFE_MIN_BORDER 16  /* EDGE_THRESHOLD-3, src/ORBextractor.cc:771 */
 #define ORBFE_NUM_STAGES 6   /* pyramid, fast, blur, quadtree, assemble, orient+describe (+2 stereo) */

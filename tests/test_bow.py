@@ -176,6 +176,26 @@ def test_gpu_transform_chained_after_extraction():
     voc.close(); ex.close()
 
 
+@pytest.mark.gpu
+def test_gpu_transform_batch_reports_frames_beyond_max_features():
+    """DBoW2 uses every feature of a frame; a device batch whose frame has more descriptors than the object holds must say so
+    (ORBFE_E_CAPACITY for that frame), not return vectors of a truncated feature set.  The other frames stay correct."""
+    import torch
+    from orb_slam3_detailed_comments_kor_b200.bow import ORBVocabulary
+    from orb_slam3_detailed_comments_kor_b200._lib import OrbfeError
+    rows = make_vocabulary(7, 10, 4)
+    voc = ORBVocabulary(10, 4, 0, 0, *rows, max_features=64, max_batch=2)
+    orc = O.OracleVocabulary(10, 4, 0, 0, *rows)
+    feats = make_features(3, rows[2], 200).reshape(2, 100, 32)
+    d_desc, d_cnt = torch.from_numpy(feats).cuda(), torch.tensor([40, 100], dtype=torch.int32, device="cuda")
+    voc.transform_batch_device(d_desc.data_ptr(), 100, d_cnt.data_ptr(), 2, 2)
+    torch.cuda.synchronize()
+    assert same(voc.result(0, 40), orc.transform(feats[0, :40], 2))
+    with pytest.raises(OrbfeError, match="max_features"):
+        voc.result(1, 64)
+    voc.close()
+
+
 # ------------------------------------------------------------------------------------------------------ SearchByBoW
 def make_pair(seed, rows, n_kf, n_f, turn=25.0):
     """A keyframe and a frame looking at the same scene: most frame descriptors are keyframe descriptors with a few bits flipped."""

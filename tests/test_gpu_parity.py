@@ -232,6 +232,47 @@ def test_host_batch_pipeline_over_several_chunks():
     ex.close()
 
 
+def test_quadtree_above_8192_nodes_per_level():
+    """A per-level quota above 8192 (50000 features: 10860 on level 0): the partial rounds sort more than 8192 nodes, which
+    the sort key has to index without aliasing.  Dense noise gives level 0 far more candidates than its quota."""
+    W, H, params = 1600, 1200, (50000, 1.2, 8, 20, 7)
+    rng = np.random.RandomState(9)
+    img = rng.randint(0, 256, (H // 2, W // 2)).astype(np.uint8).repeat(2, 0).repeat(2, 1)
+    img = (img.astype(np.int32) + rng.randint(-20, 21, (H, W))).clip(0, 255).astype(np.uint8)
+    ex = ORBextractor(*params, width=W, height=H)
+    orc = O.OracleExtractor(*params)
+    mono, kps, desc = ex(img, (0, 0))
+    omono, okps, odesc = orc(img, (0, 0))
+    assert int((okps["octave"] == 0).sum()) > 8192, "the case must exercise more than 8192 nodes on a level"
+    assert mono == omono
+    assert_same_keypoints(kps, okps, "50000 features")
+    assert np.array_equal(desc, odesc)
+    ex.close()
+
+
+def test_extractors_of_different_sizes_side_by_side():
+    """Tracking keeps mpIniORBextractor (5 x nFeatures) next to the per-frame extractors (src/Tracking.cc:1151-1157), and
+    the kernels' dynamic shared-memory limits belong to the device, not to an object: creating a small extractor after a
+    large one must not take the large one's launches away.  Large -> small -> large again, single-frame (graph) and batch paths."""
+    W, H = 752, 480
+    big_p, small_p = (5000, 1.2, 8, 20, 7), (300, 1.2, 8, 20, 7)
+    img = synth.frame(31, W, H)
+    big = ORBextractor(*big_p, width=W, height=H, max_batch=2)
+    _, k0, d0 = big(img, (0, 0))
+    small = ORBextractor(*small_p, width=W, height=H)
+    small2 = ORBextractor(*small_p, width=W // 2, height=H // 2)          # other cell sizes -> other FAST tile size
+    _, ks, ds = small(img, (0, 0))
+    _, k1, d1 = big(img, (0, 0))
+    assert np.array_equal(k0, k1) and np.array_equal(d0, d1)
+    cnt, mono, kb, db = big.extract_batch_host(np.stack([img, img]), (0, 0))
+    assert cnt[0] == len(k0) and np.array_equal(db[0][:cnt[0]], d0) and np.array_equal(db[1][:cnt[1]], d0)
+    okb, oks = O.OracleExtractor(*big_p)(img, (0, 0)), O.OracleExtractor(*small_p)(img, (0, 0))
+    assert_same_keypoints(k1, okb[1], "big")
+    assert_same_keypoints(ks, oks[1], "small")
+    assert np.array_equal(d1, okb[2]) and np.array_equal(ds, oks[2])
+    big.close(); small.close(); small2.close()
+
+
 def test_capacity_limits_are_refused_loudly():
     """What the library cannot hold (more than 16384 quadtree nodes on a level, a side above 4000 px) is an error at creation, not
     a wrong result."""

@@ -4,8 +4,9 @@ with cudaMalloc/cudaFree, or a host whose pool already owns all device memory).
 
 The new entry point is called through the C ABI twice in a row — the second time with fewer queries, another database
 size and the other TH variant, so anything left in the library's built-in scratch array by the first call would show —
-and each result is compared with the existing allocating entry point (orbfe_hamming_top2).  Integer results: the
-tolerance is zero, as everywhere else in the suite.  The file name sorts last on purpose, so a run that stops at the
+and each result is compared with the existing allocating entry point (orbfe_hamming_top2) and, because both share their
+kernels, with the CPU oracle as well.  Integer results: the tolerance is zero, as everywhere else in the suite.  Free
+device memory is read before and after the second call: it must not move.  The file name sorts last on purpose, so a run that stops at the
 first failure has already run every other test; it also passes when run on its own in a fresh process."""
 import ctypes as C
 
@@ -30,8 +31,12 @@ def _search_both_ways(L, lib, torch, db, q, th, ratio, strict, index_base):
                                       int(strict), C.c_void_p(d_out.data_ptr()), C.c_void_p(stream.cuda_stream)))
     stream.synchronize()
     got = d_out.cpu().numpy().view(MATCH_DTYPE).reshape(nq)
+    from oracle import orb_oracle as O
+    ref = O.hamming_top2(q, db, th, ratio, strict)
+    ref["idx"] += np.where(ref["idx"] >= 0, index_base, 0).astype(np.int32)
     for fld in ("best1", "best2", "idx", "accepted"):
         assert np.array_equal(got[fld], want[fld]), fld
+        assert np.array_equal(got[fld], ref[fld]), "oracle: " + fld
     return got
 
 
@@ -45,6 +50,23 @@ def test_static_scratch_entry_point_matches_allocating_one_twice_in_a_row():
     db2, q2 = synth.descriptors(42, 3001, 777)             # smaller in both dimensions, `<` variant, shard offset
     second = _search_both_ways(L, _lib, torch, db2, q2, 50, 0.9, True, 1000000)
     assert second["idx"].min() >= 1000000
+    # a further call with everything already on the device leaves the amount of free device memory where it was
+    d_q, d_db = torch.from_numpy(q2).cuda(), torch.from_numpy(db2).cuda()
+    d_out = torch.zeros((q2.shape[0], 4), dtype=torch.int32, device="cuda")
+    torch.cuda.synchronize()
+    free_before = torch.cuda.mem_get_info()[0]
+    _lib.check(L.orbfe_hamming_top2_static(0, C.c_void_p(d_q.data_ptr()), q2.shape[0], C.c_void_p(d_db.data_ptr()), db2.shape[0], 0, 50, 0.9, 0,
+                                           C.c_void_p(d_out.data_ptr()), None))
+    torch.cuda.synchronize()
+    assert torch.cuda.mem_get_info()[0] == free_before
+    # an empty database: no candidate for any query (256 / 256 / -1 / rejected), as the oracle says
+    _lib.check(L.orbfe_hamming_top2_static(0, C.c_void_p(d_q.data_ptr()), q2.shape[0], None, 0, 0, 50, 0.9, 0, C.c_void_p(d_out.data_ptr()), None))
+    torch.cuda.synchronize()
+    empty = d_out.cpu().numpy().view(_lib.MATCH_DTYPE).reshape(-1)
+    assert (empty["best1"] == 256).all() and (empty["best2"] == 256).all() and (empty["idx"] == -1).all() and not empty["accepted"].any()
+    # pointers that are not 16-byte aligned are refused
+    rc = L.orbfe_hamming_top2_static(0, C.c_void_p(d_q.data_ptr() + 4), 8, C.c_void_p(d_db.data_ptr()), 100, 0, 50, 0.9, 0, C.c_void_p(d_out.data_ptr()), None)
+    assert rc == -2 and b"aligned" in L.orbfe_last_error()
     # beyond the stated limit the call is refused with a clear message, not truncated
     big = torch.zeros((4097, 32), dtype=torch.uint8, device="cuda")
     out = torch.zeros((4097, 4), dtype=torch.int32, device="cuda")
