@@ -378,7 +378,33 @@ def main():
     for _ in range(args.steps):
         e2e_step()
     torch.cuda.synchronize()
+    e2e_sync_ms = max_over_ranks((time.perf_counter() - t0) * 1e3 / args.steps)
+    barrier()
+
+    # the same call split into submit / wait with two batches in flight: the upload of step k+1 overlaps the kernels of step k and
+    # the download of step k overlaps the kernels of step k+1 (every step still uploads its own images from pinned memory and
+    # downloads its own results; the outputs of consecutive steps go to two alternating sets of pinned arrays)
+    def pinned_out():
+        side = lambda: (np.zeros(P, np.int32), np.zeros(P, np.int32),  # noqa: E731
+                        torch.empty((P, cap, 28), dtype=torch.uint8, pin_memory=True).numpy().view(_lib.KP_DTYPE).reshape(P, cap),
+                        torch.empty((P, cap, 32), dtype=torch.uint8, pin_memory=True).numpy())
+        return side() + side() + (torch.empty((P, cap), dtype=torch.float32, pin_memory=True).numpy(), torch.empty((P, cap), dtype=torch.float32, pin_memory=True).numpy())
+    outs = [e2e_out, pinned_out()]
+
+    def e2e_pipelined(nsteps):
+        M.stereo_frames_submit(exL, exR, hLn, hRn, MBF, 0.0, FX, (0, 0), outs[0])
+        for k in range(1, nsteps):
+            M.stereo_frames_submit(exL, exR, hLn, hRn, MBF, 0.0, FX, (0, 0), outs[k & 1])
+            M.stereo_frames_wait(exL, exR, outs[(k - 1) & 1])
+        M.stereo_frames_wait(exL, exR, outs[(nsteps - 1) & 1])
+
+    e2e_pipelined(3)
+    barrier()
+    t0 = time.perf_counter()
+    e2e_pipelined(args.steps)
+    torch.cuda.synchronize()
     e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3 / args.steps)
+    assert np.array_equal(outs[0][0], outs[1][0]) and np.array_equal(outs[0][3][0], outs[1][3][0]), "the two output sets of the pipelined run disagree"
     barrier()
     # the host link's own speed for the same upload (pinned -> device), to read the e2e figure against
     t0 = time.perf_counter()
@@ -387,8 +413,11 @@ def main():
     torch.cuda.synchronize()
     h2d_gbs = 3 * 2 * P * W * H / (time.perf_counter() - t0) / 1e9
     e2e = {"value": 2 * P * world / (e2e_ms / 1e3), "unit": "frames/s", "ms_per_step": e2e_ms,
-           "call": "orbfe_stereo_frames_batch_host (pinned host images in, keypoints / descriptors / uRight / depth out)",
+           "call": "orbfe_stereo_frames_submit / _wait, two batches in flight (pinned host images in, keypoints / descriptors / uRight / depth out, every step)",
+           "one_synchronous_call_ms_per_step": e2e_sync_ms,
            "two_extract_calls_plus_stereo_ms_per_step": e2e_two_calls_ms,
+           "fraction_of_device_resident": ms_step / e2e_ms,
+           "h2d_gbs_reached_in_step": 2 * P * W * H / (e2e_ms / 1e3) / 1e9,
            "pinned_h2d_gbs_measured": h2d_gbs, "h2d_only_ms_per_step": 2 * P * W * H / h2d_gbs / 1e6,
            "h2d_bytes_per_step": 2 * P * W * H,
            "d2h_bytes_per_step": 2 * P * (cap * 60 + 8) + 2 * P * cap * 4}

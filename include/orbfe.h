@@ -107,6 +107,19 @@ int orbfe_extract_batch_host(orbfe_extractor* ex, const uint8_t* h_images, int n
 int orbfe_stereo_frames_batch_host(orbfe_extractor* exL, orbfe_extractor* exR, const uint8_t* h_left, const uint8_t* h_right, int nframes, int lap0,
                                    int lap1, float mbf, float min_d, float max_d, orbfe_keypoint* kps_l, uint8_t* desc_l, int32_t* n_l, int32_t* mono_l,
                                    orbfe_keypoint* kps_r, uint8_t* desc_r, int32_t* n_r, int32_t* mono_r, int cap, float* u_right, float* depth);
+/* The same batch call split in two, so that a stream of batches keeps the copy engines and the SMs busy at the same time (the
+ * reference has no counterpart: its Frame constructor is synchronous).  _submit enqueues the uploads, both extractions, the stereo
+ * matching and the downloads of one batch and returns at once; _wait blocks until the OLDEST submitted batch is complete on the
+ * host and then fills its counts.  Up to two batches may be in flight (a third _submit is refused with ORBFE_E_CAPACITY): the
+ * upload of batch k+1 overlaps the kernels of batch k, whose downloads overlap the kernels of batch k+1.  Typical loop:
+ *     submit(0); for k = 1..: { submit(k); wait(k-1); consume(k-1); }  wait(last);
+ * The caller passes a different set of (pinned) output arrays to batches that are in flight together and keeps the input arrays
+ * untouched until their batch has been waited for.  Between a _submit and its _wait the two extractors must not be used through
+ * any other entry point.  orbfe_stereo_frames_batch_host is _submit followed by _wait. */
+int orbfe_stereo_frames_submit(orbfe_extractor* exL, orbfe_extractor* exR, const uint8_t* h_left, const uint8_t* h_right, int nframes, int lap0, int lap1,
+                               float mbf, float min_d, float max_d, orbfe_keypoint* kps_l, uint8_t* desc_l, orbfe_keypoint* kps_r, uint8_t* desc_r, int cap,
+                               float* u_right, float* depth);
+int orbfe_stereo_frames_wait(orbfe_extractor* exL, orbfe_extractor* exR, int32_t* n_l, int32_t* mono_l, int32_t* n_r, int32_t* mono_r);
 /* Fetch what the last batch call left on the device (synchronises the object's stream). */
 int orbfe_batch_counts(orbfe_extractor* ex, int nframes, int32_t* n, int32_t* mono_index);
 int orbfe_batch_result(orbfe_extractor* ex, int frame, orbfe_keypoint* kps, uint8_t* desc, int cap, int* n,

@@ -19,11 +19,15 @@
 #include <mutex>
 
 #include "orbfe_internal.h"
+#include "orbfe_tma.cuh"
 #include "orbfe_trig.cuh"
 
 __constant__ int c_umax[16];
 __device__ __align__(16) float g_patternf[1024];   /* bit_pattern_31_ as floats: (x0,y0,x1,y1) per test */
-__constant__ uint32_t c_rowmask[32];               /* lane u-15: bit v+15 set iff |u| <= umax[|v|] */
+/* IC_Angle weights for k_orient_describe: [s = patch alignment 0..3][step 0..8][lane] -> (u weights, v weights) as four signed bytes
+ * each, zero outside the radius-15 disc.  Steps 0..7: lane = (row & 3) * 8 + word, row = 4*step + (lane >> 3); step 8: lane = row,
+ * ninth word of the row.  Byte t of a row's 36-byte window is patch column u = t - s - 15. */
+__device__ __align__(16) uint2 g_icw[4 * 9 * 32];
 
 static __device__ __forceinline__ int reflect101(int p, int n) {
     /* |overshoot| <= 19 < n: one reflection is enough (cv::copyMakeBorder BORDER_REFLECT_101) */
@@ -285,6 +289,81 @@ __global__ void __launch_bounds__(256) k_blur7(const __grid_constant__ ExDesc d,
         *reinterpret_cast<uint32_t*>(o) = oe;
         if (gy + 1 < L.h) *reinterpret_cast<uint32_t*>(o + L.bpitch) = oo;
     }
+    }
+}
+
+/* The same blur with the tile brought in by TMA: one thread issues a 3-D tensor copy (x, padded row, frame) of the
+ * 96 x 64 byte box around the tile (box rows beyond the padded level are zero-filled by the hardware; they only feed
+ * outputs below the image, which are not stored), everybody waits on the mbarrier, and both passes run from shared
+ * memory.  No per-thread address arithmetic, clamping or global loads remain; the tile (level, tx, ty) comes from a host
+ * table instead of a search over the levels and a division.  Tensor maps: one per level over this extractor's own pyramid
+ * slab (orbfe_host.cu), never over memory of another GPU, no multicast. */
+#define BLUR_SROWS (2 * BLUR_PAIRS)   /* 64 tile rows: y0-4 .. y0+59 */
+#define BLUR_SPITCH 96                /* bytes per tile row: px x0-16 .. x0+79 (the box must start on a 16-byte boundary of the row and be a multiple of
+                                         16 bytes wide; px x0-4 .. x0+67 are used) */
+__global__ void __launch_bounds__(256) k_blur7_tma(const __grid_constant__ ExDesc d, ExBuffers b, const CUtensorMap* __restrict__ maps, int frame0) {
+    __shared__ __align__(128) uint8_t s_tile[BLUR_SROWS * BLUR_SPITCH];
+    __shared__ __align__(16) uint32_t s_h[BLUR_PAIRS][BLUR_TW];
+    __shared__ __align__(8) uint64_t s_bar;
+    const uint32_t t = __ldg(b.blurTiles + blockIdx.x);
+    const int level = t >> 24, y0 = ((t >> 12) & 0xFFF) * BLUR_TH, x0 = (t & 0xFFF) * BLUR_TW;
+    const LevelDesc& L = d.lv[level];
+    if (threadIdx.x == 0) mbar_init(&s_bar, 1);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        mbar_expect_tx(&s_bar, BLUR_SROWS * BLUR_SPITCH);
+        tma_load_3d(s_tile, maps + level, &s_bar, ORBFE_ROW_LEAD + x0 - 16, y0 - 4 + ORBFE_EDGE, frame0 + (int)blockIdx.y);
+    }
+    const uint32_t KLO = 18u | (34u << 8) | (48u << 16) | (56u << 24);  /* taps -3..0 */
+    const uint32_t KHI = 48u | (34u << 8) | (18u << 16);                /* taps +1..+3 */
+    const int q = threadIdx.x & 15;
+    const int jbase = threadIdx.x >> 4;   /* the half-warps of a warp read rows two apart: 48 words = bank offset 16, conflict-free */
+    mbar_wait(&s_bar, 0);
+#pragma unroll
+    for (int sweep = 0; sweep < 2; sweep++) {
+        const int j = jbase + 16 * sweep;   /* row pair j, pixel group q (4 px) */
+        uint32_t hrow[2][4];
+#pragma unroll
+        for (int rr = 0; rr < 2; rr++) {
+            const uint32_t* p = reinterpret_cast<const uint32_t*>(s_tile + (2 * j + rr) * BLUR_SPITCH + 12) + q;
+            const uint32_t w0 = p[0], w1 = p[1], w2 = p[2];   /* px x-4..x-1 | x..x+3 | x+4..x+7 */
+            hrow[rr][0] = __dp4a(__funnelshift_r(w0, w1, 8), KLO, __dp4a(__funnelshift_r(w1, w2, 8), KHI, 0u));
+            hrow[rr][1] = __dp4a(__funnelshift_r(w0, w1, 16), KLO, __dp4a(__funnelshift_r(w1, w2, 16), KHI, 0u));
+            hrow[rr][2] = __dp4a(__funnelshift_r(w0, w1, 24), KLO, __dp4a(__funnelshift_r(w1, w2, 24), KHI, 0u));
+            hrow[rr][3] = __dp4a(w1, KLO, __dp4a(w2, KHI, 0u));
+        }
+        *reinterpret_cast<uint4*>(&s_h[j][4 * q]) = make_uint4(__byte_perm(hrow[0][0], hrow[1][0], 0x5410), __byte_perm(hrow[0][1], hrow[1][1], 0x5410),
+                                                               __byte_perm(hrow[0][2], hrow[1][2], 0x5410), __byte_perm(hrow[0][3], hrow[1][3], 0x5410));
+    }
+    __syncthreads();
+    uint8_t* dst = b.blur + (size_t)blockIdx.y * d.blurSlab + L.blurOff;
+    /* one item = output rows (y0+2m, y0+2m+1) x 4 pixels; needs pairs m .. m+4 (rows y0+2m-4 .. y0+2m+5) */
+#pragma unroll
+    for (int sweep = 0; sweep < (BLUR_TH / 2 + 15) / 16; sweep++) {
+        const int m = (threadIdx.x >> 4) + 16 * sweep;
+        const int gy = y0 + 2 * m, gx = x0 + 4 * q;
+        if (m < BLUR_TH / 2 && gy < L.h && gx < L.bpitch) {
+            uint4 pr[5];
+#pragma unroll
+            for (int k = 0; k < 5; k++) pr[k] = *reinterpret_cast<const uint4*>(&s_h[m + k][4 * q]);
+            /* even row y: rows y-3..y+3 = (pair0.hi) (pair1) (pair2) (pair3); odd row y+1: (pair1) (pair2) (pair3) (pair4.lo) */
+            const uint32_t E0 = 18u << 8, E1 = 34u | (48u << 8), E2 = 56u | (48u << 8), E3 = 34u | (18u << 8);
+            const uint32_t O1 = 18u | (34u << 8), O2 = 48u | (56u << 8), O3 = 48u | (34u << 8), O4 = 18u;
+            const uint32_t* P0 = &pr[0].x; const uint32_t* P1 = &pr[1].x; const uint32_t* P2 = &pr[2].x;
+            const uint32_t* P3 = &pr[3].x; const uint32_t* P4 = &pr[4].x;
+            uint32_t ve[4], vo[4];
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                ve[k] = __dp2a_lo(P0[k], E0, __dp2a_lo(P1[k], E1, __dp2a_lo(P2[k], E2, __dp2a_lo(P3[k], E3, 32768u))));
+                vo[k] = __dp2a_lo(P1[k], O1, __dp2a_lo(P2[k], O2, __dp2a_lo(P3[k], O3, __dp2a_lo(P4[k], O4, 32768u))));
+            }
+            /* byte 2 of each Q16.16 sum is the output pixel (sums < 2^24) */
+            const uint32_t oe = __byte_perm(__byte_perm(ve[0], ve[1], 0x0062), __byte_perm(ve[2], ve[3], 0x0062), 0x5410);
+            const uint32_t oo = __byte_perm(__byte_perm(vo[0], vo[1], 0x0062), __byte_perm(vo[2], vo[3], 0x0062), 0x5410);
+            uint8_t* o = dst + (uint32_t)(gy * L.bpitch + gx);
+            *reinterpret_cast<uint32_t*>(o) = oe;
+            if (gy + 1 < L.h) *reinterpret_cast<uint32_t*>(o + L.bpitch) = oo;
+        }
     }
 }
 
@@ -1200,25 +1279,24 @@ __global__ void __launch_bounds__(OD_NT) k_orient_describe(const __grid_constant
     const int l = wk.y & 0xFF, slot = wk.y >> 8;
     const LevelDesc& L = d.lv[l];
 
-    /* IC_Angle, src/ORBextractor.cc:75-102: m10 = sum u*I, m01 = sum v*I over the disc */
-    const int u = lane - 15;
+    /* IC_Angle, src/ORBextractor.cc:75-102: m10 = sum u*I, m01 = sum v*I over the disc.  The 31 x 31 box is read as aligned
+     * words, four rows of eight words per step (a request covers four 32-byte runs) plus one step for the ninth word of every
+     * row; each word meets its two weight words (u and v per byte, 0 outside the disc) in two DP4A. */
     const int pitch = L.pitch;
-    const uint8_t* p = b.pyr + f * d.pyrSlab + (uint32_t)(L.pyrOff + (y + ORBFE_EDGE - 15) * pitch + ORBFE_ROW_LEAD + x + u);
-    const uint32_t rows = c_rowmask[lane];
-    /* all 31 rows are fetched unconditionally (the 31 x 32 box around a keypoint is always inside the padded level), so
-     * the loads go out back to back; rows outside the disc are masked afterwards */
-    int pv[31];
+    const int xb = ORBFE_ROW_LEAD + x - 15, s = xb & 3;
+    const uint8_t* p = b.pyr + f * d.pyrSlab + (uint32_t)(L.pyrOff + (y + ORBFE_EDGE - 15 + (lane >> 3)) * pitch + (xb - s) + 4 * (lane & 7));
+    const uint2* wt = g_icw + s * (9 * 32) + lane;
+    uint32_t px[9];
 #pragma unroll
-    for (int v = 0; v < 31; v++) pv[v] = __ldg(p + v * pitch);
-    asm volatile("" ::: "memory");   /* keep the 31 loads ahead of their uses: one memory round trip, not 31 */
-    int colsum = 0, m01 = 0;
+    for (int k = 0; k < 8; k++) px[k] = __ldg(reinterpret_cast<const uint32_t*>(p + k * 4 * pitch));   /* rows 4k + (lane >> 3); row 31 has weight 0 */
+    px[8] = __ldg(reinterpret_cast<const uint32_t*>(b.pyr + f * d.pyrSlab + (uint32_t)(L.pyrOff + (y + ORBFE_EDGE - 15 + min(lane, 30)) * pitch + (xb - s) + 32)));
+    int m10 = 0, m01 = 0;
 #pragma unroll
-    for (int v = 0; v < 31; v++) {
-        const int val = (rows >> v) & 1u ? pv[v] : 0;
-        colsum += val;
-        m01 += (v - 15) * val;
+    for (int k = 0; k < 9; k++) {
+        const uint2 w = __ldg(wt + 32 * k);
+        asm("dp4a.s32.u32 %0, %1, %2, %0;" : "+r"(m10) : "r"(w.x), "r"(px[k]));
+        asm("dp4a.s32.u32 %0, %1, %2, %0;" : "+r"(m01) : "r"(w.y), "r"(px[k]));
     }
-    int m10 = u * colsum;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
         m10 += __shfl_xor_sync(0xFFFFFFFFu, m10, o);
@@ -1260,17 +1338,23 @@ int orbfe_upload_constants(const int* umax16, const int8_t* pattern1024) {
     for (int lane = 0; lane < 32; lane++)
         for (int k = 0; k < 8; k++)
             for (int c = 0; c < 4; c++) pf[(k * 32 + lane) * 4 + c] = (float)pattern1024[(lane * 8 + k) * 4 + c];
-    uint32_t rowmask[32];
-    for (int lane = 0; lane < 32; lane++) {
-        const int u = lane - 15, au = u < 0 ? -u : u;
-        uint32_t m = 0;
-        for (int v = -15; v <= 15; v++)
-            if (lane < 31 && au <= umax16[v < 0 ? -v : v]) m |= 1u << (v + 15);
-        rowmask[lane] = m;
-    }
     ORBFE_CUDA(cudaMemcpyToSymbol(c_umax, umax16, 16 * sizeof(int)));
     ORBFE_CUDA(cudaMemcpyToSymbol(g_patternf, pf, sizeof pf));
-    ORBFE_CUDA(cudaMemcpyToSymbol(c_rowmask, rowmask, sizeof rowmask));
+    static uint2 icw[4 * 9 * 32];
+    for (int sft = 0; sft < 4; sft++)
+        for (int k = 0; k < 9; k++)
+            for (int lane = 0; lane < 32; lane++) {
+                const int row = k < 8 ? 4 * k + (lane >> 3) : lane, word = k < 8 ? (lane & 7) : 8;
+                uint32_t wu = 0, wv = 0;
+                for (int bt = 0; bt < 4; bt++) {
+                    const int u = 4 * word + bt - sft - 15, v = row - 15;
+                    if (row > 30 || u < -15 || u > 15 || (u < 0 ? -u : u) > umax16[v < 0 ? -v : v]) continue;
+                    wu |= (uint32_t)(uint8_t)(int8_t)u << (8 * bt);
+                    wv |= (uint32_t)(uint8_t)(int8_t)v << (8 * bt);
+                }
+                icw[(sft * 9 + k) * 32 + lane] = make_uint2(wu, wv);
+            }
+    ORBFE_CUDA(cudaMemcpyToSymbol(g_icw, icw, sizeof icw));
     ORBFE_CUDA(orbfe_trig_init());
     return 0;
 }
@@ -1361,7 +1445,8 @@ int orbfe_launch_extract(orbfe_extractor* ex, const uint8_t* d_images, int nfram
     k_fast_nms<<<dim3((d.nCells + FN_WARPS - 1) / FN_WARPS, nframes), FN_WARPS * 32, 0, st>>>(d, xb);
     k_fast_cells_list<<<148 * 8, FAST_NT, ex->fastSmem, st>>>(d, xb);
     STAGE_MARK();
-    k_blur7<<<dim3(d.blurTile0[d.nlevels], nframes), 256, 0, st>>>(d, xb);
+    if (ex->blurLdg) k_blur7<<<dim3(d.blurTile0[d.nlevels], nframes), 256, 0, st>>>(d, xb);
+    else k_blur7_tma<<<dim3(d.blurTile0[d.nlevels], nframes), 256, 0, st>>>(d, xb, ex->blurMaps, frame0);
     STAGE_MARK();
     if (d.qtScratchBytes) k_quadtree<true><<<dim3(d.nlevels, nframes), QT_NT, 0, st>>>(d, xb);
     else k_quadtree<false><<<dim3(d.nlevels, nframes), QT_NT, ex->quadSmem, st>>>(d, xb);

@@ -1,6 +1,7 @@
 /* orbfe_internal.h — shared declarations of liborbfe.so (not installed; the public surface is include/orbfe.h). */
 #ifndef ORBFE_INTERNAL_H
 #define ORBFE_INTERNAL_H
+#include <cuda.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <string>
@@ -94,6 +95,7 @@ struct ExBuffers {
     int* fbList;         /* [B*nCells]    cells that came out empty at iniTh */
     int* fbCount;        /* [1] */
     const StripDesc* strips;
+    const uint32_t* blurTiles; /* [blurTile0[nlevels]] level << 24 | tile row << 12 | tile column, in launch order */
     uint32_t* keys;      /* [B][candCap]  quadtree scratch: a level's candidates gathered in cell order */
     uint16_t* keyNode;   /* [B][candCap]  quadtree scratch: node of each candidate */
     uint32_t* sel;       /* [B][kpCap]    quadtree output, packed like cand, per level at selBase */
@@ -125,11 +127,18 @@ struct orbfe_extractor {
     cudaStream_t stream;
     cudaStream_t copyIn, copyOut;          /* host-batch pipeline: uploads and downloads overlap the kernels */
     std::vector<cudaEvent_t> evIn, evDone; /* one pair per chunk of hostChunk frames */
+    std::vector<cudaEvent_t> evOut;        /* per chunk: the download of its results has finished (next batch may rewrite them) */
+    std::vector<char> evOutValid;
+    cudaEvent_t evBatch[2];                /* per submit slot: everything of that batch is on the host */
+    uint8_t* inputStage2;                  /* second image staging buffer (slot 1 of orbfe_stereo_frames_submit), allocated on first use */
+    int pendingHead, pendingCount, pendingFrames[2];
     int hostChunk;                         /* frames per pipeline stage (ORBFE_HOST_CHUNK, or env ORBFE_HOST_CHUNK) */
     std::vector<float> scale, invScale, sigma2, invSigma2;
     std::vector<int> quota, umax;
     std::vector<void*> allocs;
     int fastSmem, quadSmem;
+    CUtensorMap* blurMaps;   /* device array, one 3-D map (x bytes, padded rows, frames) per level over b.pyr, for k_blur7_tma */
+    int blurLdg;             /* ORBFE_BLUR_LDG=1: the pre-TMA blur kernel (A/B measurements) */
     /* optional per-stage timing (orbfe_set_profiling): events bracket each stage of the last launch */
     int profiling;
     cudaEvent_t ev[ORBFE_NUM_STAGES + 3];

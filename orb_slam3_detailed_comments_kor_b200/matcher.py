@@ -107,6 +107,23 @@ def stereo_frames_batch_host(exL, exR, left, right, mbf, minD, maxD, vLappingAre
     return out
 
 
+def stereo_frames_submit(exL, exR, left, right, mbf, minD, maxD, vLappingArea, out):
+    """orbfe_stereo_frames_submit: enqueue one batch and return (at most two in flight).  left / right / every array of `out` (the
+    tuple stereo_frames_batch_host returns) must stay alive and untouched until the matching stereo_frames_wait; pinned memory
+    makes the copies asynchronous."""
+    nf, cap = left.shape[0], exL.capacity
+    cl, ml, kl, dl, cr, mr, kr, dr, u, d = out
+    check(_lib.lib().orbfe_stereo_frames_submit(exL.handle, exR.handle, ptr(left), ptr(right), nf, int(vLappingArea[0]), int(vLappingArea[1]),
+                                                C.c_float(mbf), C.c_float(minD), C.c_float(maxD), ptr(kl), ptr(dl), ptr(kr), ptr(dr), cap, ptr(u), ptr(d)))
+
+
+def stereo_frames_wait(exL, exR, out):
+    """orbfe_stereo_frames_wait: block until the oldest submitted batch is on the host; fills the count arrays of `out`."""
+    cl, ml, kl, dl, cr, mr, kr, dr, u, d = out
+    check(_lib.lib().orbfe_stereo_frames_wait(exL.handle, exR.handle, ptr(cl), ptr(ml), ptr(cr), ptr(mr)))
+    return out
+
+
 def stereo_result(exL, frame):
     u = np.zeros(exL.capacity, np.float32)
     d = np.zeros(exL.capacity, np.float32)

@@ -365,6 +365,47 @@ def test_stereo_frames_pipeline_matches_separate_calls():
     exL.close(); exR.close()
 
 
+def test_stereo_frames_submit_wait_keeps_two_batches_in_flight():
+    """orbfe_stereo_frames_submit / _wait: four different batches streamed with two in flight (two alternating output sets) give,
+    batch by batch, what the synchronous call gives; a third submit without a wait is refused; wait without a batch is an error."""
+    import torch
+    W, H, params, nb = 320, 240, (500, 1.2, 8, 20, 7), 70                  # 70 pairs = two chunks, one of them short
+    batches = []
+    for bi in range(4):
+        pairs = [synth.stereo_pair(900 + 100 * bi + i, W, H) for i in range(nb)]
+        batches.append((torch.from_numpy(np.stack([p[0] for p in pairs])).pin_memory().numpy(), torch.from_numpy(np.stack([p[1] for p in pairs])).pin_memory().numpy()))
+    exL = ORBextractor(*params, width=W, height=H, max_batch=nb)
+    exR = ORBextractor(*params, width=W, height=H, max_batch=nb)
+    want = [[a.copy() for a in M.stereo_frames_batch_host(exL, exR, Lb, Rb, 40.0, 0.0, 300.0, (0, 0))] for Lb, Rb in batches]
+    cap = exL.capacity
+
+    def out_set():
+        side = lambda: (np.zeros(nb, np.int32), np.zeros(nb, np.int32), np.zeros((nb, cap), KP_DTYPE), np.zeros((nb, cap, 32), np.uint8))  # noqa: E731
+        return side() + side() + (np.zeros((nb, cap), np.float32), np.zeros((nb, cap), np.float32))
+    outs = [out_set(), out_set()]
+    got = []
+    M.stereo_frames_submit(exL, exR, batches[0][0], batches[0][1], 40.0, 0.0, 300.0, (0, 0), outs[0])
+    for k in range(1, 4):
+        M.stereo_frames_submit(exL, exR, batches[k][0], batches[k][1], 40.0, 0.0, 300.0, (0, 0), outs[k & 1])
+        if k == 1:
+            with pytest.raises(OrbfeError):
+                M.stereo_frames_submit(exL, exR, batches[2][0], batches[2][1], 40.0, 0.0, 300.0, (0, 0), outs[0])
+        got.append([a.copy() for a in M.stereo_frames_wait(exL, exR, outs[(k - 1) & 1])])
+    got.append([a.copy() for a in M.stereo_frames_wait(exL, exR, outs[1])])
+    with pytest.raises(OrbfeError):
+        M.stereo_frames_wait(exL, exR, outs[0])
+    for bi in range(4):
+        cl, ml, kl, dl, cr, mr, kr, dr, u, d = got[bi]
+        wl = want[bi]
+        assert np.array_equal(cl, wl[0]) and np.array_equal(ml, wl[1]) and np.array_equal(cr, wl[4]) and np.array_equal(mr, wl[5]), "batch %d" % bi
+        for f in range(nb):
+            assert np.array_equal(kl[f, :cl[f]], wl[2][f, :cl[f]]) and np.array_equal(dl[f, :cl[f]], wl[3][f, :cl[f]]), "batch %d left %d" % (bi, f)
+            assert np.array_equal(kr[f, :cr[f]], wl[6][f, :cr[f]]) and np.array_equal(dr[f, :cr[f]], wl[7][f, :cr[f]]), "batch %d right %d" % (bi, f)
+            assert np.array_equal(u[f, :cl[f]], wl[8][f, :cl[f]]) and np.array_equal(d[f, :cl[f]], wl[9][f, :cl[f]]), "batch %d stereo %d" % (bi, f)
+    assert not np.array_equal(got[0][3], got[1][3])                      # the batches really differ
+    exL.close(); exR.close()
+
+
 def test_kitti_full_size_batch_properties():
     """BASELINE config 4 at full size: 4096 KITTI-shaped images (2048 stereo pairs, 1241x376, 2000 features) in one device
     batch per camera.  The batch is 16 distinct pairs repeated in a scrambled order: every frame must give exactly what its
