@@ -1,13 +1,16 @@
-/* ORBmatcher.h (orbfe shim) — the descriptor-matching core of ORB_SLAM3::ORBmatcher and Frame with the
- * reference's signatures (/root/reference/include/ORBmatcher.h:35-111, include/Frame.h:114,304).
+/* orbfe_matching.h (orbfe shim) — the GPU bodies of the descriptor-matching members of ORB_SLAM3::ORBmatcher and Frame, as free
+ * functions in namespace ORB_SLAM3::orbfe that take what those members read (/root/reference/include/ORBmatcher.h:35-111,
+ * include/Frame.h:114,304).
  *
- * Only the hot-path members are provided: the constants, the constructor, the static DescriptorDistance, the
- * brute-force top-2 core that SearchByBoW's inner loops perform (src/ORBmatcher.cc:311-375, 870-908), and free
- * functions carrying the bodies of Frame::ComputeStereoMatches / ComputeStereoFishEyeMatches's matching step and of
- * SearchByProjection(Frame&, vpMapPoints, th, ...) (src/ORBmatcher.cc:44-214).
+ * This header deliberately does NOT declare a class named ORBmatcher and is not called ORBmatcher.h: the reference's own
+ * include/ORBmatcher.h (with SearchByProjection x5, SearchByBoW x2, Fuse x2, SearchBySim3, SearchForTriangulation_, ... that
+ * Tracking, LocalMapping, LoopClosing, KeyFrame, MapPoint, Sim3Solver and Initializer call) stays in the build untouched; the
+ * bodies of a few of its members, and of two Frame members, become one-line calls into the functions below (INTEGRATION.md
+ * §3-§5 gives each replacement).  Only include/orbfe_shim/ORBextractor.h replaces a reference header, because it reproduces
+ * that header's whole public surface.
  * The full SearchByBoW / SearchForTriangulation / Fuse searches are C-ABI entry points (include/orbfe.h). */
-#ifndef ORBFE_SHIM_ORBMATCHER_H
-#define ORBFE_SHIM_ORBMATCHER_H
+#ifndef ORBFE_SHIM_MATCHING_H
+#define ORBFE_SHIM_MATCHING_H
 
 #include <stdexcept>
 #include <string>
@@ -16,54 +19,43 @@
 #include "ORBextractor.h"
 
 namespace ORB_SLAM3 {
+namespace orbfe {
 
-class ORBmatcher {
-public:
-    ORBmatcher(float nnratio = 0.6, bool checkOri = true) : mfNNratio(nnratio), mbCheckOrientation(checkOri) {}
+/* Body of ORBmatcher::DescriptorDistance, src/ORBmatcher.cc:2591-2607.  One 256-bit pair: eight popcounts on the host — launching
+ * a kernel for 32 bytes would cost more than the answer; the batched form is orbfe_descriptor_distances(). */
+inline int DescriptorDistance(const cv::Mat& a, const cv::Mat& b) {
+    const uint32_t* pa = a.ptr<uint32_t>();
+    const uint32_t* pb = b.ptr<uint32_t>();
+    int dist = 0;
+    for (int i = 0; i < 8; i++) dist += __builtin_popcount(pa[i] ^ pb[i]);
+    return dist;
+}
 
-    /* src/ORBmatcher.cc:2591-2607.  One 256-bit pair: eight popcounts on the host — launching a kernel for 32 bytes
-     * would cost more than the answer; the batched form is orbfe_descriptor_distances(). */
-    static int DescriptorDistance(const cv::Mat& a, const cv::Mat& b) {
-        const uint32_t* pa = a.ptr<uint32_t>();
-        const uint32_t* pb = b.ptr<uint32_t>();
-        int dist = 0;
-        for (int i = 0; i < 8; i++) dist += __builtin_popcount(pa[i] ^ pb[i]);
-        return dist;
-    }
-
-    /* The top-2 core of SearchByBoW over whole descriptor matrices (rows x 32, CV_8U): for every query row the two
-     * smallest distances, the lowest best row, and the TH_LOW + mfNNratio verdict.  kfkf selects `best1 < TH_LOW`
-     * (src/ORBmatcher.cc:906) instead of `<=` (:373). */
-    int SearchTop2(const cv::Mat& queries, const cv::Mat& database, std::vector<orbfe_match>& out, bool kfkf = false, int device = 0) const {
-        out.resize(queries.rows);
-        std::vector<unsigned char> q((size_t)queries.rows * 32), db((size_t)database.rows * 32);
-        for (int i = 0; i < queries.rows; i++) std::memcpy(&q[(size_t)i * 32], queries.ptr<unsigned char>(i), 32);
-        for (int i = 0; i < database.rows; i++) std::memcpy(&db[(size_t)i * 32], database.ptr<unsigned char>(i), 32);
-        if (orbfe_hamming_top2(device, q.data(), queries.rows, db.data(), database.rows, TH_LOW, mfNNratio, kfkf ? 1 : 0, out.data()) != ORBFE_OK)
-            throw std::runtime_error(std::string("orbfe_hamming_top2: ") + orbfe_last_error());
-        int n = 0;
-        for (const orbfe_match& m : out) n += m.accepted;
-        return n;
-    }
-
-    static const int TH_LOW = 50;
-    static const int TH_HIGH = 100;
-    static const int HISTO_LENGTH = 30;
-
-protected:
-    float mfNNratio;
-    bool mbCheckOrientation;
-};
+/* The top-2 core of SearchByBoW over whole descriptor matrices (rows x 32, CV_8U): for every query row the two smallest
+ * distances, the lowest best row, and the thLow (ORBmatcher::TH_LOW) + nnratio (mfNNratio) verdict.  kfkf selects
+ * `best1 < TH_LOW` (src/ORBmatcher.cc:906) instead of `<=` (:373). */
+inline int SearchTop2(const cv::Mat& queries, const cv::Mat& database, std::vector<orbfe_match>& out, float nnratio, int thLow = 50, bool kfkf = false,
+                      int device = 0) {
+    out.resize(queries.rows);
+    std::vector<unsigned char> q((size_t)queries.rows * 32), db((size_t)database.rows * 32);
+    for (int i = 0; i < queries.rows; i++) std::memcpy(&q[(size_t)i * 32], queries.ptr<unsigned char>(i), 32);
+    for (int i = 0; i < database.rows; i++) std::memcpy(&db[(size_t)i * 32], database.ptr<unsigned char>(i), 32);
+    if (orbfe_hamming_top2(device, q.data(), queries.rows, db.data(), database.rows, thLow, nnratio, kfkf ? 1 : 0, out.data()) != ORBFE_OK)
+        throw std::runtime_error(std::string("orbfe_hamming_top2: ") + orbfe_last_error());
+    int n = 0;
+    for (const orbfe_match& m : out) n += m.accepted;
+    return n;
+}
 
 /* Body of Frame::ComputeStereoMatches (src/Frame.cc:797-967) for the frames the two extractors processed last.
- * mb is uninitialised in the reference when this runs (src/Frame.cc:827 vs :173); the intended maxD = mbf/mb = fx
- * is therefore an explicit argument.  mvuRight / mvDepth are resized to N and filled (-1 = no match). */
-inline void ComputeStereoMatches(ORBextractor* left, ORBextractor* right, int N, float mbf, float fx,
+ * The reference's maxD is mbf/mb with mb = mbf/fx (src/Frame.cc:827-829, :173); pass that float as maxD (it equals fx for the
+ * EuRoC and KITTI settings).  mvuRight / mvDepth are resized to N and filled (-1 = no match). */
+inline void ComputeStereoMatches(ORBextractor* left, ORBextractor* right, int N, float mbf, float maxD,
                                  std::vector<float>& mvuRight, std::vector<float>& mvDepth) {
     mvuRight.assign(N, -1.0f);
     mvDepth.assign(N, -1.0f);
     if (N == 0) return;
-    if (orbfe_stereo_match_batch_device(left->Impl(), right->Impl(), 1, mbf, 0.0f, fx, nullptr) != ORBFE_OK)
+    if (orbfe_stereo_match_batch_device(left->Impl(), right->Impl(), 1, mbf, 0.0f, maxD, nullptr) != ORBFE_OK)
         throw std::runtime_error(std::string("orbfe_stereo_match: ") + orbfe_last_error());
     int n = 0;
     if (orbfe_stereo_result(left->Impl(), 0, mvuRight.data(), mvDepth.data(), N, &n) != ORBFE_OK)
@@ -115,5 +107,6 @@ inline int SearchByProjection(const std::vector<cv::KeyPoint>& keys, const cv::M
     return nmatches;
 }
 
+}  // namespace orbfe
 }  // namespace ORB_SLAM3
 #endif

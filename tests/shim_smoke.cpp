@@ -3,9 +3,38 @@
 #include <cstdio>
 #include <cstdlib>
 #include <vector>
-#include "orbfe_shim/ORBmatcher.h"
+#include "orbfe_shim/ORBextractor.h"     // replaces the reference's include/ORBextractor.h (same public surface)
+#include "orbfe_shim/orbfe_matching.h"   // next to the reference's own ORBmatcher.h / Frame.h, which stay as they are
 extern "C" int orbfe_synth_stereo(uint64_t frame_index, int W, int H, uint8_t* left, uint8_t* right);
 using namespace ORB_SLAM3;
+
+// Stand-ins for the reference's own declarations (include/ORBmatcher.h:42,95-97; include/Frame.h:114 and the members the body
+// reads), followed by the member bodies exactly as INTEGRATION.md section 3 and 5 give them.
+namespace ORB_SLAM3 {
+class ORBmatcher {
+public:
+    ORBmatcher(float nnratio = 0.6, bool checkOri = true) : mfNNratio(nnratio), mbCheckOrientation(checkOri) {}
+    static int DescriptorDistance(const cv::Mat& a, const cv::Mat& b);
+    static const int TH_LOW;
+    static const int TH_HIGH;
+    float mfNNratio;
+    bool mbCheckOrientation;
+};
+const int ORBmatcher::TH_HIGH = 100;
+const int ORBmatcher::TH_LOW = 50;
+class Frame {
+public:
+    void ComputeStereoMatches();
+    int N;
+    float mbf, mb;
+    ORBextractor *mpORBextractorLeft, *mpORBextractorRight;
+    std::vector<float> mvuRight, mvDepth;
+};
+// src/ORBmatcher.cc:2591-2607
+int ORBmatcher::DescriptorDistance(const cv::Mat& a, const cv::Mat& b) { return orbfe::DescriptorDistance(a, b); }
+// src/Frame.cc:797-967
+void Frame::ComputeStereoMatches() { orbfe::ComputeStereoMatches(mpORBextractorLeft, mpORBextractorRight, N, mbf, mbf / mb, mvuRight, mvDepth); }
+}  // namespace ORB_SLAM3
 int main(int argc, char** argv) {
     const int W = 752, H = 480;
     cv::Mat imL(H, W, CV_8UC1), imR(H, W, CV_8UC1), mask;
@@ -16,14 +45,17 @@ int main(int argc, char** argv) {
     std::vector<int> lap = {0, 0};
     const int monoL = left(imL, mask, kL, dL, lap);                           // src/Frame.cc:413-420
     const int monoR = right(imR, mask, kR, dR, lap);
-    std::vector<float> uR, depth;
-    ComputeStereoMatches(&left, &right, (int)kL.size(), 47.90639f, 435.2047f, uR, depth);
+    Frame F;
+    F.N = (int)kL.size(); F.mbf = 47.90639f; F.mb = F.mbf / 435.2047f;           // src/Frame.cc:173
+    F.mpORBextractorLeft = &left; F.mpORBextractorRight = &right;
+    F.ComputeStereoMatches();
+    const std::vector<float>& uR = F.mvuRight;
     int matched = 0;
     for (float v : uR) matched += v >= 0;
     const int d01 = ORBmatcher::DescriptorDistance(dL.row(0), dL.row(1));
     ORBmatcher m(0.9f, true);
     std::vector<orbfe_match> res;
-    const int acc = m.SearchTop2(dL, dR, res);
+    const int acc = orbfe::SearchTop2(dL, dR, res, m.mfNNratio, ORBmatcher::TH_LOW);
     // Tracking::SearchLocalPoints-like: every left keypoint re-projected half a pixel off as a map point (src/ORBmatcher.cc:44-214)
     std::vector<orbfe_proj_query> pq(kL.size());
     for (size_t i = 0; i < kL.size(); i++) {
@@ -33,7 +65,7 @@ int main(int argc, char** argv) {
     }
     std::vector<unsigned char> taken;
     std::vector<orbfe_proj_match> pm;
-    const int proj = SearchByProjection(kL, dL, -1, &uR, nullptr, taken, 0.f, 0.f, 64.f / W, 48.f / H, pq, dL, 0.8f, pm);
+    const int proj = orbfe::SearchByProjection(kL, dL, -1, &uR, nullptr, taken, 0.f, 0.f, 64.f / W, 48.f / H, pq, dL, 0.8f, pm);
     int projSelf = 0;
     for (size_t i = 0; i < pm.size(); i++) projSelf += pm[i].accepted && pm[i].best_idx == (int)i;
     cv::Mat empty;

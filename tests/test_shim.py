@@ -16,6 +16,29 @@ def test_shim_compiles_without_opencv():
                            os.path.join(ROOT, "tests", "shim_smoke.cpp")])
 
 
+REFERENCE_HEADERS = ["Atlas.h", "Config.h", "Converter.h", "Frame.h", "FrameDrawer.h", "G2oTypes.h", "ImuTypes.h", "Initializer.h", "KeyFrame.h",
+                     "KeyFrameDatabase.h", "LocalMapping.h", "LoopClosing.h", "MLPnPsolver.h", "Map.h", "MapDrawer.h", "MapPoint.h", "ORBVocabulary.h",
+                     "ORBextractor.h", "ORBmatcher.h", "OptimizableTypes.h", "Optimizer.h", "PnPsolver.h", "Sim3Solver.h", "System.h", "Tracking.h",
+                     "TwoViewReconstruction.h", "Viewer.h"]   # /root/reference/include (absent on the GPU box, hence the list)
+
+
+def test_shim_directory_shadows_only_the_header_it_fully_replaces():
+    """INTEGRATION.md puts include/orbfe_shim in front of the reference's include/.  Every file there that carries the name of a
+    reference header replaces that header for ALL of its includers, so only a complete stand-in may use such a name: that is
+    ORBextractor.h (whole public surface of include/ORBextractor.h:43-109) and nothing else — in particular no ORBmatcher.h."""
+    ref_inc = "/root/reference/include"
+    names = set(REFERENCE_HEADERS)
+    if os.path.isdir(ref_inc):
+        found = {f for f in os.listdir(ref_inc) if f.endswith(".h")}
+        assert found == names, "reference headers the list above does not know: %s" % sorted(found - names)
+    shim = set(os.listdir(os.path.join(ROOT, "include", "orbfe_shim")))
+    assert shim & names == {"ORBextractor.h"}
+    src = open(os.path.join(ROOT, "include", "orbfe_shim", "ORBextractor.h")).read()
+    for member in ("ORBextractor(int nfeatures, float scaleFactor, int nlevels", "operator()", "GetLevels", "GetScaleFactor", "GetScaleFactors",
+                   "GetInverseScaleFactors", "GetScaleSigmaSquares", "GetInverseScaleSigmaSquares", "mvImagePyramid"):
+        assert member in src, member
+
+
 @pytest.mark.gpu
 def test_shim_matches_oracle(tmp_path):
     from oracle import orb_oracle as O
