@@ -467,16 +467,30 @@ def main():
     torch.cuda.synchronize()
     ham_out = [d_out]
 
-    def ham_step():
-        if world == 1:
-            shard.top2_device(d_q.data_ptr(), nq, 50, 0.9, False, d_out.data_ptr(), st)
-        else:
-            shard.top2_device(d_q.data_ptr(), nq, 50, 0.9, False, d_part.data_ptr(), st)
-            gathered = sharding.gather_top2(d_part, world)            # NCCL all-gather on the current (timed) stream
-            ham_out[0] = sharding.merge_gathered(gathered, 50, 0.9, False, device=local_rank, stream=st)
+    comm = sharding.create_nccl_comm(rank, world, local_rank)
+
+    def ham_step():   # the C entry point: shard search, ncclAllGather, merge on one stream (no Python between them)
+        shard.top2_sharded(comm, world, d_q.data_ptr(), nq, 50, 0.9, False, d_out.data_ptr(), st)
+
+    def ham_step_harness():   # the same through torch.distributed (round 1's path), kept as a cross-check and a comparison
+        shard.top2_device(d_q.data_ptr(), nq, 50, 0.9, False, d_part.data_ptr(), st)
+        gathered = sharding.gather_top2(d_part, world)
+        return sharding.merge_gathered(gathered, 50, 0.9, False, device=local_rank, stream=st)
 
     for _ in range(3):
         ham_step()
+    harness_ms = None
+    if world > 1:
+        check_out = ham_step_harness()
+        torch.cuda.synchronize()
+        assert torch.equal(check_out, d_out), "orbfe_hamming_top2_sharded disagrees with the torch.distributed all-gather + merge"
+        barrier()
+        e0.record()
+        for _ in range(args.steps):
+            ham_step_harness()
+        e1.record()
+        barrier()
+        harness_ms = max_over_ranks(e0.elapsed_time(e1) / args.steps)
     barrier()
     e0.record()
     for _ in range(args.steps):
@@ -488,6 +502,8 @@ def main():
     popc_peak = 148 * 16 * float(peaks.get("sm_max_mhz", 1965.0)) * 1e6 / 8.0   # pairs/s/GPU at 8 POPC per pair
     hamming = {"value": pairs_s, "unit": "descriptor_pairs/s", "ms_per_step": ham_ms, "scaling": "strong",
                "queries": nq, "db_rows": ndb, "shards": world, "accepted": int(ham_out[0][:, 3].sum().item()),
+               "call": "orbfe_hamming_top2_sharded (shard search + ncclAllGather + merge enqueued by one C call)",
+               "torch_distributed_all_gather_path_ms": harness_ms,
                "roofline": {"bound": "int_popc", "achieved": pairs_s / world, "peak": popc_peak, "unit": "pairs/s/GPU",
                             "frac": pairs_s / world / popc_peak,
                             "peak_source": "148 SM x 16 POPC/clk x sm_max_mhz / 8 POPC per pair (nominal; SURVEY.md §8d)",
@@ -606,6 +622,7 @@ def main():
                 "hamming": hamming}
         print(json.dumps(line), flush=True)
     if world > 1:
+        sharding.destroy_nccl_comm(comm)
         dist.destroy_process_group()
 
 

@@ -184,6 +184,21 @@ int orbfe_matcher_top2_device(orbfe_matcher* m, const uint8_t* d_queries, int nq
  * reference is single-process. */
 int orbfe_top2_merge_device(int device, const orbfe_match* d_parts, int nshards, int nq, int th, float ratio,
                             int strict_lt, orbfe_match* d_out, void* stream);
+/* The sharded search in one call (new: the reference is single-process; this is what a multi-GPU
+ * LoopClosing::DetectCommonRegionsFromBoW-style search, src/LoopClosing.cc:681-725, calls from C++): `m` holds THIS rank's shard
+ * (rows [index_base, index_base + rows), set with orbfe_matcher_set_db*); the call searches it, all-gathers the nq 16-byte records of
+ * every rank with ncclAllGather on `nccl_comm` (an ncclComm_t of `nranks` ranks whose rank order is ascending index_base) and
+ * merges them into d_out[nq] exactly as one scan of the whole database would (ties to the lowest global row): search, collective
+ * and merge are enqueued on `stream` (NULL = the object's stream) with no host synchronisation in between.  nranks == 1 needs no
+ * communicator (with one, the one-rank collective still runs).  The first call allocates the gather buffers (nranks x max_queries records).  NCCL is resolved with dlopen
+ * (libnccl.so.2, or $ORBFE_NCCL_LIB); ORBFE_E_NCCL when it is missing or a collective fails.  Every rank must make the call. */
+int orbfe_hamming_top2_sharded(orbfe_matcher* m, void* nccl_comm, int nranks, const uint8_t* d_queries, int nq, int th, float ratio,
+                               int strict_lt, orbfe_match* d_out, void* stream);
+/* Convenience for hosts without their own NCCL bootstrap: rank 0 calls orbfe_nccl_unique_id, ships the 128 bytes to the other
+ * ranks by any means, every rank calls orbfe_nccl_comm_create (collective) and later orbfe_nccl_comm_destroy. */
+int orbfe_nccl_unique_id(uint8_t id128[128]);
+int orbfe_nccl_comm_create(int device, int nranks, int rank, const uint8_t id128[128], void** comm);
+int orbfe_nccl_comm_destroy(void* comm);
 /* The top-2 search for callers that cannot allocate (no counterpart in the reference; it has no GPU memory to
  * manage).  Meant for ORB-SLAM3's per-frame Tracking thread, which runs against a frame deadline while LocalMapping
  * and LoopClosing use the same GPU: cudaMalloc/cudaFree lock the device and cudaFree waits for all of it, so that

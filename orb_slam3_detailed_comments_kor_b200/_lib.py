@@ -47,6 +47,10 @@ SIGNATURES = {
     "orbfe_stereo_frames_batch_host": (i32, [vp, vp, vp, vp, i32, i32, i32, C.c_float, C.c_float, C.c_float, vp, vp, vp, vp, vp, vp, vp, vp, i32, vp, vp]),
     "orbfe_stereo_frames_submit": (i32, [vp, vp, vp, vp, i32, i32, i32, C.c_float, C.c_float, C.c_float, vp, vp, vp, vp, i32, vp, vp]),
     "orbfe_stereo_frames_wait": (i32, [vp, vp, vp, vp, vp, vp]),
+    "orbfe_hamming_top2_sharded": (i32, [vp, vp, i32, vp, i32, i32, f32, i32, vp, vp]),
+    "orbfe_nccl_unique_id": (i32, [vp]),
+    "orbfe_nccl_comm_create": (i32, [i32, i32, i32, vp, C.POINTER(vp)]),
+    "orbfe_nccl_comm_destroy": (i32, [vp]),
     "orbfe_batch_counts": (i32, [vp, i32, vp, vp]),
     "orbfe_batch_result": (i32, [vp, i32, vp, vp, i32, C.POINTER(i32), C.POINTER(i32)]),
     "orbfe_batch_device_views": (i32, [vp, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]),

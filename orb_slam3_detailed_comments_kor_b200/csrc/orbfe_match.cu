@@ -8,11 +8,13 @@
  * The Hamming work is XOR + POPC on the integer pipe (8 x 32-bit per 256-bit pair); it is deliberately not
  * reshaped into a tensor-core contraction (BASELINE.json north_star). */
 #include <cuda_runtime.h>
+#include <dlfcn.h>
 #include <limits.h>
 #include <stdint.h>
 #include <string.h>
 
 #include <algorithm>
+#include <mutex>
 #include <new>
 
 #include "orbfe_internal.h"
@@ -151,6 +153,9 @@ struct orbfe_matcher {
     orbfe_match* dOut;
     int maxSlices;
     cudaStream_t stream;
+    orbfe_match* dGather;  /* [gatherRanks][maxQ] all-gathered per-shard records of orbfe_hamming_top2_sharded, allocated on first use */
+    orbfe_match* dLocal;   /* [maxQ] this shard's records (the all-gather's send buffer) */
+    int gatherRanks;
 };
 
 static int top2_plan(long long ndb, int nq, int maxSlices, int* rowsPerSlice) {
@@ -492,6 +497,8 @@ void orbfe_matcher_destroy(orbfe_matcher* m) {
     cudaFree(m->dQ);
     cudaFree(m->dParts);
     cudaFree(m->dOut);
+    cudaFree(m->dGather);
+    cudaFree(m->dLocal);
     if (m->stream) cudaStreamDestroy(m->stream);
     delete m;
 }
@@ -545,6 +552,119 @@ int orbfe_matcher_top2_device(orbfe_matcher* m, const uint8_t* d_queries, int nq
     ORBFE_CUDA(cudaSetDevice(m->device));
     return launch_top2(d_queries, nq, m->dDb, m->ndb, m->indexBase, m->dParts, m->maxSlices, th, ratio, 0.0, strict_lt ? 1 : 0,
                        d_out, stream ? (cudaStream_t)stream : m->stream);
+}
+
+/* ---- the sharded search: local top-2, NCCL all-gather of the per-shard records, merge — one stream, no host
+ * round trip in between.  NCCL is looked up at run time (dlopen of the libnccl.so.2 the process already uses, e.g. the one torch
+ * loaded, else the system one), so liborbfe.so itself has no link-time dependency on it. */
+namespace {
+typedef int (*nccl_allgather_fn)(const void*, void*, size_t, int /*ncclDataType_t*/, void* /*ncclComm_t*/, cudaStream_t);
+typedef const char* (*nccl_errstr_fn)(int);
+typedef int (*nccl_uid_fn)(void*);
+typedef struct { char internal[128]; } nccl_uid;   /* ncclUniqueId, nccl.h: NCCL_UNIQUE_ID_BYTES = 128 */
+typedef int (*nccl_init_fn)(void**, int, nccl_uid, int);
+typedef int (*nccl_destroy_fn)(void*);
+struct NcclApi {
+    void* lib = nullptr;
+    nccl_allgather_fn allGather = nullptr;
+    nccl_errstr_fn errStr = nullptr;
+    nccl_uid_fn uniqueId = nullptr;
+    nccl_init_fn initRank = nullptr;
+    nccl_destroy_fn destroy = nullptr;
+};
+std::mutex g_nccl_mu;
+NcclApi g_nccl;
+int nccl_api(NcclApi** out) {
+    std::lock_guard<std::mutex> lk(g_nccl_mu);
+    if (!g_nccl.lib) {
+        const char* names[] = {getenv("ORBFE_NCCL_LIB"), "libnccl.so.2", "libnccl.so"};
+        for (const char* n : names) {
+            if (!n || !*n) continue;
+            g_nccl.lib = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
+            if (g_nccl.lib) break;
+        }
+        if (!g_nccl.lib) { orbfe_set_error("NCCL library not found (libnccl.so.2; set ORBFE_NCCL_LIB): %s", dlerror()); return ORBFE_E_NCCL; }
+        g_nccl.allGather = (nccl_allgather_fn)dlsym(g_nccl.lib, "ncclAllGather");
+        g_nccl.errStr = (nccl_errstr_fn)dlsym(g_nccl.lib, "ncclGetErrorString");
+        g_nccl.uniqueId = (nccl_uid_fn)dlsym(g_nccl.lib, "ncclGetUniqueId");
+        g_nccl.initRank = (nccl_init_fn)dlsym(g_nccl.lib, "ncclCommInitRank");
+        g_nccl.destroy = (nccl_destroy_fn)dlsym(g_nccl.lib, "ncclCommDestroy");
+        if (!g_nccl.allGather || !g_nccl.errStr || !g_nccl.uniqueId || !g_nccl.initRank || !g_nccl.destroy) {
+            g_nccl.lib = nullptr;
+            orbfe_set_error("the NCCL library lacks ncclAllGather / ncclCommInitRank");
+            return ORBFE_E_NCCL;
+        }
+    }
+    *out = &g_nccl;
+    return 0;
+}
+int nccl_fail(NcclApi* api, int rc, const char* what) {
+    orbfe_set_error("NCCL error %d (%s) in %s", rc, api->errStr ? api->errStr(rc) : "?", what);
+    return ORBFE_E_NCCL;
+}
+}  // namespace
+
+int orbfe_nccl_unique_id(uint8_t id128[128]) {
+    NcclApi* api = nullptr;
+    int rc = nccl_api(&api);
+    if (rc) return rc;
+    if (!id128) { orbfe_set_error("bad argument"); return ORBFE_E_INVALID; }
+    nccl_uid u;
+    rc = api->uniqueId(&u);
+    if (rc) return nccl_fail(api, rc, "ncclGetUniqueId");
+    memcpy(id128, u.internal, 128);
+    return ORBFE_OK;
+}
+
+int orbfe_nccl_comm_create(int device, int nranks, int rank, const uint8_t id128[128], void** comm) {
+    NcclApi* api = nullptr;
+    int rc = nccl_api(&api);
+    if (rc) return rc;
+    if (!id128 || !comm || nranks < 1 || rank < 0 || rank >= nranks) { orbfe_set_error("bad argument"); return ORBFE_E_INVALID; }
+    ORBFE_CUDA(cudaSetDevice(device));
+    nccl_uid u;
+    memcpy(u.internal, id128, 128);
+    *comm = nullptr;
+    rc = api->initRank(comm, nranks, u, rank);
+    if (rc) return nccl_fail(api, rc, "ncclCommInitRank");
+    return ORBFE_OK;
+}
+
+int orbfe_nccl_comm_destroy(void* comm) {
+    NcclApi* api = nullptr;
+    int rc = nccl_api(&api);
+    if (rc) return rc;
+    if (comm) { rc = api->destroy(comm); if (rc) return nccl_fail(api, rc, "ncclCommDestroy"); }
+    return ORBFE_OK;
+}
+
+int orbfe_hamming_top2_sharded(orbfe_matcher* m, void* nccl_comm, int nranks, const uint8_t* d_queries, int nq, int th, float ratio, int strict_lt,
+                               orbfe_match* d_out, void* stream) {
+    if (!m || !d_queries || !d_out || nq < 1 || nranks < 1 || (nranks > 1 && !nccl_comm)) { orbfe_set_error("bad argument"); return ORBFE_E_INVALID; }
+    if (nq > m->maxQ) { orbfe_set_error("%d queries exceed capacity %d", nq, m->maxQ); return ORBFE_E_CAPACITY; }
+    if (((uintptr_t)d_queries & 15) != 0) { orbfe_set_error("query pointer must be 16-byte aligned"); return ORBFE_E_INVALID; }
+    ORBFE_CUDA(cudaSetDevice(m->device));
+    cudaStream_t st = stream ? (cudaStream_t)stream : m->stream;
+    if (nranks == 1 && !nccl_comm) return launch_top2(d_queries, nq, m->dDb, m->ndb, m->indexBase, m->dParts, m->maxSlices, th, ratio, 0.0, strict_lt ? 1 : 0, d_out, st);
+    NcclApi* api = nullptr;
+    int rc = nccl_api(&api);
+    if (rc) return rc;
+    if (m->gatherRanks < nranks) {   /* first sharded call (or a larger communicator): the gather buffers */
+        ORBFE_CUDA(cudaStreamSynchronize(st));
+        cudaFree(m->dGather); m->dGather = nullptr;
+        if (!m->dLocal) ORBFE_CUDA(cudaMalloc((void**)&m->dLocal, (size_t)m->maxQ * sizeof(orbfe_match)));
+        ORBFE_CUDA(cudaMalloc((void**)&m->dGather, (size_t)nranks * m->maxQ * sizeof(orbfe_match)));
+        m->gatherRanks = nranks;
+    }
+    /* this shard's top-2 (global row indices; the threshold verdict is recomputed by the merge) */
+    rc = launch_top2(d_queries, nq, m->dDb, m->ndb, m->indexBase, m->dParts, m->maxSlices, th, ratio, 0.0, strict_lt ? 1 : 0, m->dLocal, st);
+    if (rc) return rc;
+    /* rank r's nq records land at dGather[r*nq ..]: ascending rank = ascending global row, the order the merge scans */
+    const int nrc = api->allGather(m->dLocal, m->dGather, (size_t)nq * sizeof(orbfe_match), 0 /* ncclInt8 */, nccl_comm, st);
+    if (nrc) return nccl_fail(api, nrc, "ncclAllGather");
+    k_top2_merge<<<(nq + 127) / 128, 128, 0, st>>>(m->dGather, nranks, nq, th, ratio, 0.0, strict_lt ? 1 : 0, 1, 256, d_out);
+    ORBFE_CUDA(cudaGetLastError());
+    return ORBFE_OK;
 }
 
 int orbfe_matcher_top2(orbfe_matcher* m, const uint8_t* h_queries, int nq, int th, float ratio, int strict_lt, orbfe_match* h_out) {
@@ -681,7 +801,6 @@ int orbfe_distinctive_descriptors(int device, const uint8_t* desc, const int32_t
 #define ORBFE_STATIC_MAX_SLICES 64
 static __device__ __align__(256) orbfe_match g_static_parts[(size_t)ORBFE_STATIC_MAX_SLICES * ORBFE_STATIC_MAX_QUERIES];
 
-#include <mutex>
 static std::mutex g_static_mu;
 static orbfe_match* g_static_addr[64]; /* per device ordinal, filled on first use */
 

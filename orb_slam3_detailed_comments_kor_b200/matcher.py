@@ -50,6 +50,12 @@ class DescriptorDatabase:
                                                 C.c_void_p(stream) if stream else None))
 
 
+    def top2_sharded(self, comm, nranks, d_q, nq, th, ratio, strict_lt, d_out, stream=None):
+        """orbfe_hamming_top2_sharded: this shard's search, ncclAllGather of every rank's records and the merge, all on `stream`."""
+        check(self._L.orbfe_hamming_top2_sharded(self._h, C.c_void_p(comm) if comm else None, nranks, C.c_void_p(d_q), nq, th, ratio, int(strict_lt),
+                                                 C.c_void_p(d_out), C.c_void_p(stream) if stream else None))
+
+
 class ORBmatcher:
     TH_HIGH = 100       # src/ORBmatcher.cc:36
     TH_LOW = 50         # src/ORBmatcher.cc:37

@@ -43,3 +43,33 @@ def merge_gathered(gathered, th, ratio, strict_lt, device=None, stream=None):
     M.merge_top2_device(gathered.device.index if device is None else device, gathered.data_ptr(), world, nq, th, ratio,
                         strict_lt, out.data_ptr(), stream)
     return out
+
+
+def create_nccl_comm(rank, world, device):
+    """An ncclComm_t for orbfe_hamming_top2_sharded (the C entry point takes the communicator of its C++ host; this harness has
+    torch.distributed, whose communicator is not reachable from Python, so it bootstraps a second one): rank 0 draws the unique
+    id, torch.distributed broadcasts the 128 bytes, every rank joins.  Returns the handle as an int (0 when world == 1)."""
+    import ctypes as C
+    import torch
+    import torch.distributed as dist
+    from . import _lib
+    if world == 1:
+        return 0
+    L = _lib.lib()
+    buf = (C.c_uint8 * 128)()
+    if rank == 0:
+        _lib.check(L.orbfe_nccl_unique_id(buf))
+    dev = "cuda" if dist.get_backend() == "nccl" else "cpu"
+    t = torch.tensor(list(buf), dtype=torch.uint8, device=dev)
+    dist.broadcast(t, 0)
+    raw = bytes(t.cpu().tolist())
+    ident = (C.c_uint8 * 128).from_buffer_copy(raw)
+    comm = C.c_void_p()
+    _lib.check(L.orbfe_nccl_comm_create(device, world, rank, ident, C.byref(comm)))
+    return comm.value
+
+
+def destroy_nccl_comm(comm):
+    from . import _lib
+    if comm:
+        _lib.check(_lib.lib().orbfe_nccl_comm_destroy(comm))

@@ -523,6 +523,38 @@ def test_top2_full_size_properties_and_sharding():
     assert np.array_equal(host["idx"], full["idx"]) and np.array_equal(host["accepted"], full["accepted"])
 
 
+def test_sharded_search_entry_point_single_rank():
+    """orbfe_hamming_top2_sharded on one GPU: without a communicator (plain search) and through a real one-rank NCCL communicator
+    (dlopen of NCCL, ncclAllGather of the shard's records, merge) — both equal the oracle, index_base included.  The multi-rank
+    case is checked by bench.py under torchrun against the torch.distributed path (profiles/r2_bench_2gpu.json)."""
+    import ctypes as C
+    import torch
+    from orb_slam3_detailed_comments_kor_b200 import _lib
+    nq, ndb, base = 700, 50000, 123456
+    db, q = synth.descriptors(77, ndb, nq)
+    want = O.hamming_top2(q, db, 50, 0.9, True)
+    want["idx"] += np.where(want["idx"] >= 0, base, 0).astype(np.int32)
+    shard = M.DescriptorDatabase(ndb, nq)
+    shard.set(db, index_base=base)
+    d_q, d_out = torch.from_numpy(q).cuda(), torch.zeros((nq, 4), dtype=torch.int32, device="cuda")
+    L = _lib.lib()
+    ident, comm = (C.c_uint8 * 128)(), C.c_void_p()
+    _lib.check(L.orbfe_nccl_unique_id(ident))
+    _lib.check(L.orbfe_nccl_comm_create(0, 1, 0, ident, C.byref(comm)))
+    for handle in (None, comm.value):
+        d_out.zero_()
+        torch.cuda.synchronize()
+        shard.top2_sharded(handle, 1, d_q.data_ptr(), nq, 50, 0.9, True, d_out.data_ptr())
+        torch.cuda.synchronize()
+        got = d_out.cpu().numpy().view(O.MATCH_DTYPE).reshape(nq)
+        for fld in ("best1", "best2", "idx", "accepted"):
+            assert np.array_equal(got[fld], want[fld]), (fld, handle)
+    _lib.check(L.orbfe_nccl_comm_destroy(comm))
+    with pytest.raises(OrbfeError):
+        shard.top2_sharded(None, 2, d_q.data_ptr(), nq, 50, 0.9, True, d_out.data_ptr())   # two ranks need a communicator
+    shard.close()
+
+
 @pytest.mark.parametrize("name", ["tumvi", "noise"])
 def test_knn2_matches_oracle_and_golden(name):
     g = np.load(os.path.join(GOLD, name + ".npz"))
