@@ -432,6 +432,21 @@ def main():
         ex1(one)
     single_ms = (time.perf_counter() - t0) * 1e3 / 20
     ex1.close()
+    # the same frame through the C++ drop-in as shipped (include/orbfe_shim/ORBextractor.h::operator(), compiled from
+    # tests/shim_smoke.cpp by build()): with the eight mvImagePyramid host mirrors, and built with -DORBFE_SHIM_LAZY_PYRAMID
+    shim_ms = {}
+    if rank == 0:
+        import re
+        import subprocess
+        pkg = os.path.join(ROOT, "orb_slam3_detailed_comments_kor_b200")
+        for key, exe in (("pyramid_mirrored", "shim_probe.bin"), ("pyramid_lazy", "shim_probe_lazy.bin")):
+            try:
+                out = subprocess.run([os.path.join(pkg, exe), "--latency", "200"], capture_output=True, text=True, timeout=120,
+                                     env=dict(os.environ, CUDA_VISIBLE_DEVICES=os.environ.get("CUDA_VISIBLE_DEVICES", str(local_rank)))).stdout
+                shim_ms[key] = float(re.search(r"shim_latency_us=([\d.]+)", out).group(1)) / 1e3
+            except Exception as exc:   # the probe is optional evidence, not part of the timed region
+                shim_ms[key] = None
+                shim_ms["error"] = repr(exc)[:200]
 
     # ---- input conditioning: rectification of the same frames, device to device
     from orb_slam3_detailed_comments_kor_b200.conditioning import Rectifier
@@ -617,7 +632,7 @@ def main():
                            "l2": "inputs_larger_than_L2 (%d MB of images per step per GPU)" % (2 * P * W * H >> 20),
                            "mean_keypoints_per_frame": nkp, "parallelism": "frames sharded by rank, no collective"},
                 "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
-                "single_frame_latency_ms": single_ms, "rectify": rectify, "projection": projection, "bow": bow,
+                "single_frame_latency_ms": single_ms, "shim_single_frame_latency_ms": shim_ms, "rectify": rectify, "projection": projection, "bow": bow,
                 "gpu_launches": (2 * (PARAMS[2] + 8) + 3) * args.steps,
                 "hamming": hamming}
         print(json.dumps(line), flush=True)

@@ -132,6 +132,13 @@ int orbfe_batch_device_views(orbfe_extractor* ex, const orbfe_keypoint** d_kps, 
 /* Host mirrors of ORBextractor::mvImagePyramid (include/ORBextractor.h:83; read by src/Frame.cc:804,894-909)
  * and stage-level views used by the parity tests.  padded != 0 returns the (h+38)x(w+38) bordered buffer. */
 int orbfe_pyramid_level(orbfe_extractor* ex, int frame, int level, int padded, uint8_t* dst);
+/* All levels of one frame in one call (what the shim's mvImagePyramid mirrors need after every operator()): dst_levels[l] receives
+ * level l like orbfe_pyramid_level would (NULL entries are skipped); the border kernel and the copies share one wait. */
+int orbfe_pyramid_levels(orbfe_extractor* ex, int frame, int padded, uint8_t* const* dst_levels);
+/* Page-lock / release a host buffer the caller keeps reusing as a download target (cudaHostRegister / cudaHostUnregister): the
+ * copies into it then run at link speed and without a staging copy.  The shim pins its mvImagePyramid mirrors with it. */
+int orbfe_pin_host(void* p, size_t bytes);
+int orbfe_unpin_host(void* p);
 int orbfe_blurred_level(orbfe_extractor* ex, int frame, int level, uint8_t* dst);
 /* vToDistributeKeys of one level (src/ORBextractor.cc:846-850): x, y (relative to the 16 px border), response. */
 int orbfe_fast_candidates(orbfe_extractor* ex, int frame, int level, orbfe_keypoint* out, int cap, int* n);

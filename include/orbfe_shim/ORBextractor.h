@@ -52,7 +52,10 @@ public:
         }
         mvImagePyramid.resize(nlevels);
     }
-    ~ORBextractor() { if (mpImpl) orbfe_extractor_destroy(mpImpl); }
+    ~ORBextractor() {
+        for (unsigned char* p : mvPinned) if (p) orbfe_unpin_host(p);
+        if (mpImpl) orbfe_extractor_destroy(mpImpl);
+    }
     ORBextractor(const ORBextractor&) = delete;
     ORBextractor& operator=(const ORBextractor&) = delete;
 
@@ -100,16 +103,23 @@ public:
     /* orbfe additions (not in the reference): the device object, for the stereo shim; and the pyramid fetch */
     orbfe_extractor* Impl() { return mpImpl; }
     void FetchPyramid() {
+        /* like the reference, each level is an ROI of a bordered buffer (19 px), so reads slightly outside stay valid */
+        mvPadded.resize(nlevels);
+        std::vector<unsigned char*> dst(nlevels);
+        std::vector<int> ws(nlevels), hs(nlevels);
+        mvPinned.resize(nlevels, nullptr);
         for (int l = 0; l < nlevels; l++) {
-            int w = 0, h = 0;
-            orbfe_level_size(mpImpl, l, &w, &h);
-            /* like the reference, each level is an ROI of a bordered buffer (19 px), so reads slightly outside stay valid */
-            mvPadded.resize(nlevels);
-            mvPadded[l].create(h + 38, w + 38, CV_8U);
-            if (orbfe_pyramid_level(mpImpl, 0, l, 1, mvPadded[l].ptr<unsigned char>(0)) != ORBFE_OK)
-                throw std::runtime_error(std::string("orbfe_pyramid_level: ") + orbfe_last_error());
-            mvImagePyramid[l] = cv::Mat(h, w, CV_8U, mvPadded[l].ptr<unsigned char>(19) + 19, mvPadded[l].step);
+            orbfe_level_size(mpImpl, l, &ws[l], &hs[l]);
+            mvPadded[l].create(hs[l] + 38, ws[l] + 38, CV_8U);
+            dst[l] = mvPadded[l].ptr<unsigned char>(0);
+            if (mvPinned[l] != dst[l]) {   /* the mirrors are reused frame after frame: page-lock them once, the downloads run at link speed */
+                if (mvPinned[l]) orbfe_unpin_host(mvPinned[l]);
+                mvPinned[l] = orbfe_pin_host(dst[l], (size_t)(hs[l] + 38) * (ws[l] + 38)) == ORBFE_OK ? dst[l] : nullptr;
+            }
         }
+        if (orbfe_pyramid_levels(mpImpl, 0, 1, dst.data()) != ORBFE_OK)
+            throw std::runtime_error(std::string("orbfe_pyramid_levels: ") + orbfe_last_error());
+        for (int l = 0; l < nlevels; l++) mvImagePyramid[l] = cv::Mat(hs[l], ws[l], CV_8U, mvPadded[l].ptr<unsigned char>(19) + 19, mvPadded[l].step);
     }
 
 protected:
@@ -134,6 +144,7 @@ protected:
     std::vector<orbfe_keypoint> mvKeyBuf;
     std::vector<unsigned char> mvDescBuf;
     std::vector<cv::Mat> mvPadded;
+    std::vector<unsigned char*> mvPinned;
 };
 
 }  // namespace ORB_SLAM3

@@ -39,6 +39,7 @@ public:
     Mat(int r, int c, int type) { create(r, c, type); }
     Mat(int r, int c, int type, void* ext, size_t stp = 0) : rows(r), cols(c), step(stp ? stp : (size_t)c * esz(type)), data((unsigned char*)ext), type_(type) {}
     void create(int r, int c, int type) {
+        if (store_ && data == store_.get() && r == rows && c == cols && type == type_) return;   /* like cv::Mat::create: same shape keeps the buffer */
         rows = r; cols = c; type_ = type; step = (size_t)c * esz(type);
         store_ = std::shared_ptr<unsigned char>(new unsigned char[step * (size_t)(r > 0 ? r : 1)], std::default_delete<unsigned char[]>());
         data = store_.get();

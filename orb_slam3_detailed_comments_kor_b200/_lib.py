@@ -55,6 +55,9 @@ SIGNATURES = {
     "orbfe_batch_result": (i32, [vp, i32, vp, vp, i32, C.POINTER(i32), C.POINTER(i32)]),
     "orbfe_batch_device_views": (i32, [vp, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]),
     "orbfe_pyramid_level": (i32, [vp, i32, i32, i32, vp]),
+    "orbfe_pyramid_levels": (i32, [vp, i32, i32, vp]),
+    "orbfe_pin_host": (i32, [vp, sz]),
+    "orbfe_unpin_host": (i32, [vp]),
     "orbfe_blurred_level": (i32, [vp, i32, i32, vp]),
     "orbfe_fast_candidates": (i32, [vp, i32, i32, vp, i32, C.POINTER(i32)]),
     "orbfe_stereo_match_batch_device": (i32, [vp, vp, i32, f32, f32, f32, vp]),

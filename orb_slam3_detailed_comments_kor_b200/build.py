@@ -28,7 +28,25 @@ def build(force=False, verbose=False):
         subprocess.check_call(cmd)
     from . import synth
     synth.build(force)
+    build_shim_probe(force)
     return LIB
+
+
+SHIM_PROBES = {"shim_probe": [], "shim_probe_lazy": ["-DORBFE_SHIM_LAZY_PYRAMID"]}
+
+
+def build_shim_probe(force=False):
+    """tests/shim_smoke.cpp compiled against the C++ drop-in headers (include/orbfe_shim) and liborbfe.so: bench.py runs it with
+    --latency to time ORBextractor::operator() as a C++ caller sees it, with the mvImagePyramid mirrors and without."""
+    root = os.path.dirname(_HERE)
+    src = os.path.join(root, "tests", "shim_smoke.cpp")
+    deps = [src, os.path.join(root, "include", "orbfe_shim", "ORBextractor.h"), os.path.join(root, "include", "orbfe_shim", "orbfe_matching.h"),
+            os.path.join(root, "include", "orbfe_shim", "opencv_min.hpp"), os.path.join(root, "include", "orbfe.h"), LIB]
+    for name, flags in SHIM_PROBES.items():
+        exe = os.path.join(_HERE, name + ".bin")
+        if force or _stale(exe, deps):
+            subprocess.check_call(["g++", "-std=c++17", "-O2"] + flags + ["-I" + os.path.join(root, "include"), src, "-o", exe, "-L" + _HERE, "-lorbfe",
+                                   "-L" + os.path.join(_HERE, "synth"), "-lsynth", "-Wl,-rpath,$ORIGIN", "-Wl,-rpath,$ORIGIN/synth"])
 
 
 if __name__ == "__main__":

@@ -34,6 +34,7 @@ struct orbfe_vocabulary {
     /* results of the last batch (device), frame stride = maxFeatures */
     int *featWord, *featNode, *featLeaf;
     int *bowWords, *bowCount, *fvNodes, *fvStarts, *fvFeats, *fvCount;
+    cudaEvent_t evLast;   /* behind the last transform, on whichever stream ran it: the getter waits for this, not for the device */
     double* bowValues;
     uint8_t* stage; int* stageCount;   /* staging for the host entry point */
     cudaStream_t stream;
@@ -501,6 +502,7 @@ void orbfe_vocabulary_destroy(orbfe_vocabulary* v) {
     void* bufs[] = {v->childStart, v->childList, v->desc, v->weight, v->wordId, v->featWord, v->featNode, v->featLeaf, v->bowWords, v->bowCount,
                     v->fvNodes, v->fvStarts, v->fvFeats, v->fvCount, v->bowValues, v->stage, v->stageCount};
     for (void* b : bufs) cudaFree(b);
+    if (v->evLast) cudaEventDestroy(v->evLast);
     if (v->stream) cudaStreamDestroy(v->stream);
     delete v;
 }
@@ -542,6 +544,7 @@ int orbfe_vocabulary_create(int device, int k, int L, int scoring, int weighting
     memcpy(nw.data() + 1, weight, (size_t)nrows * sizeof(double));
     const size_t fr = (size_t)max_batch * max_features;
     cudaError_t e = cudaStreamCreateWithFlags(&v->stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&v->evLast, cudaEventDisableTiming);
 #define BOW_ALLOC(p, bytes) if (e == cudaSuccess) e = cudaMalloc((void**)&(p), (bytes))
     BOW_ALLOC(v->childStart, (size_t)(nn + 1) * 4); BOW_ALLOC(v->childList, (size_t)std::max(nrows, 1) * 4); BOW_ALLOC(v->desc, (size_t)nn * 32);
     BOW_ALLOC(v->weight, (size_t)nn * 8); BOW_ALLOC(v->wordId, (size_t)nn * 4);
@@ -578,6 +581,7 @@ int orbfe_bow_transform_batch_device(orbfe_vocabulary* v, const uint8_t* d_desc,
     k_bow_assemble<<<nframes, BOW_NT, (size_t)P * 12, st>>>(d_counts, F, v->weight, v->weighting, bow_norm_of(v->scoring), v->featWord, v->featNode, v->featLeaf,
                                                            v->bowWords, v->bowValues, v->bowCount, v->fvNodes, v->fvStarts, v->fvFeats, v->fvCount);
     ORBFE_CUDA(cudaGetLastError());
+    ORBFE_CUDA(cudaEventRecord(v->evLast, st));
     return ORBFE_OK;
 }
 
@@ -585,28 +589,33 @@ int orbfe_bow_result(orbfe_vocabulary* v, int frame, int nfeatures, int32_t* wor
                      int32_t* nbow, int32_t* fv_nodes, int32_t* fv_starts, int32_t* fv_feats, int32_t* nfv) {
     if (!v || frame < 0 || frame >= v->maxBatch || nfeatures < 0 || nfeatures > v->maxFeatures) { orbfe_set_error("bad argument"); return ORBFE_E_INVALID; }
     ORBFE_CUDA(cudaSetDevice(v->device));
-    ORBFE_CUDA(cudaDeviceSynchronize());
+    ORBFE_CUDA(cudaEventSynchronize(v->evLast));
+#define BOW_D2H(dst, src, bytes) ORBFE_CUDA(cudaMemcpyAsync((dst), (src), (bytes), cudaMemcpyDeviceToHost, v->stream))
     const size_t fo = (size_t)frame * v->maxFeatures, so = (size_t)frame * (v->maxFeatures + 1);
     int nb = 0, nn = 0;
-    ORBFE_CUDA(cudaMemcpy(&nb, v->bowCount + frame, 4, cudaMemcpyDeviceToHost));
-    ORBFE_CUDA(cudaMemcpy(&nn, v->fvCount + frame, 4, cudaMemcpyDeviceToHost));
+    BOW_D2H(&nb, v->bowCount + frame, 4);
+    BOW_D2H(&nn, v->fvCount + frame, 4);
+    ORBFE_CUDA(cudaStreamSynchronize(v->stream));
     if (nb < 0 || nn < 0) {
         orbfe_set_error("frame %d of the batch has more than max_features = %d descriptors: its BoW vectors were not computed", frame, v->maxFeatures);
         return ORBFE_E_CAPACITY;
     }
     if (nbow) *nbow = nb;
     if (nfv) *nfv = nn;
-    if (word_ids && nfeatures) ORBFE_CUDA(cudaMemcpy(word_ids, v->featWord + fo, (size_t)nfeatures * 4, cudaMemcpyDeviceToHost));
-    if (node_ids && nfeatures) ORBFE_CUDA(cudaMemcpy(node_ids, v->featNode + fo, (size_t)nfeatures * 4, cudaMemcpyDeviceToHost));
-    if (bow_words && nb) ORBFE_CUDA(cudaMemcpy(bow_words, v->bowWords + fo, (size_t)nb * 4, cudaMemcpyDeviceToHost));
-    if (bow_values && nb) ORBFE_CUDA(cudaMemcpy(bow_values, v->bowValues + fo, (size_t)nb * 8, cudaMemcpyDeviceToHost));
-    if (fv_nodes && nn) ORBFE_CUDA(cudaMemcpy(fv_nodes, v->fvNodes + fo, (size_t)nn * 4, cudaMemcpyDeviceToHost));
-    if (fv_starts) ORBFE_CUDA(cudaMemcpy(fv_starts, v->fvStarts + so, (size_t)(nn + 1) * 4, cudaMemcpyDeviceToHost));
+    if (word_ids && nfeatures) BOW_D2H(word_ids, v->featWord + fo, (size_t)nfeatures * 4);
+    if (node_ids && nfeatures) BOW_D2H(node_ids, v->featNode + fo, (size_t)nfeatures * 4);
+    if (bow_words && nb) BOW_D2H(bow_words, v->bowWords + fo, (size_t)nb * 4);
+    if (bow_values && nb) BOW_D2H(bow_values, v->bowValues + fo, (size_t)nb * 8);
+    if (fv_nodes && nn) BOW_D2H(fv_nodes, v->fvNodes + fo, (size_t)nn * 4);
+    if (fv_starts) BOW_D2H(fv_starts, v->fvStarts + so, (size_t)(nn + 1) * 4);
     if (fv_feats && nn) {
         int total = 0;
-        ORBFE_CUDA(cudaMemcpy(&total, v->fvStarts + so + nn, 4, cudaMemcpyDeviceToHost));
-        if (total) ORBFE_CUDA(cudaMemcpy(fv_feats, v->fvFeats + fo, (size_t)total * 4, cudaMemcpyDeviceToHost));
+        BOW_D2H(&total, v->fvStarts + so + nn, 4);
+        ORBFE_CUDA(cudaStreamSynchronize(v->stream));
+        if (total) BOW_D2H(fv_feats, v->fvFeats + fo, (size_t)total * 4);
     }
+    ORBFE_CUDA(cudaStreamSynchronize(v->stream));
+#undef BOW_D2H
     return ORBFE_OK;
 }
 
@@ -714,7 +723,7 @@ int orbfe_search_by_bow(int device, const uint8_t* desc_kf, const orbfe_keypoint
         rc = orbfe_search_by_bow_device(device, 1, S, (const int32_t*)(d + oPair), (const int32_t*)(d + oPair) + 1, d + oDesc, (const orbfe_keypoint*)(d + oKps), S,
                                         (const int32_t*)(d + oNodes), (const int32_t*)(d + oStarts), (const int32_t*)(d + oFeats), (const int32_t*)(d + oCount),
                                         d + oMp, (const int32_t*)(d + oLeft), th_low, nnratio, check_orientation, kf_kf, (int32_t*)(d + oMatch), (orbfe_match*)(d + oKf), (int32_t*)(d + oNm), nullptr);
-    if (rc == ORBFE_OK && e == cudaSuccess) e = cudaDeviceSynchronize();
+    if (rc == ORBFE_OK && e == cudaSuccess) e = cudaStreamSynchronize(nullptr);   /* the launch above went to the default stream */
     if (rc == ORBFE_OK && e == cudaSuccess && n_f) e = cudaMemcpy(match_f, d + oMatch, (size_t)n_f * 4, cudaMemcpyDeviceToHost);
     if (rc == ORBFE_OK && e == cudaSuccess && kf_out && n_kf) e = cudaMemcpy(kf_out, d + oKf, (size_t)n_kf * sizeof(orbfe_match), cudaMemcpyDeviceToHost);
     if (rc == ORBFE_OK && e == cudaSuccess && nmatches) e = cudaMemcpy(nmatches, d + oNm, 4, cudaMemcpyDeviceToHost);
@@ -797,7 +806,7 @@ int orbfe_search_for_triangulation(int device, const uint8_t* desc_1, const orbf
                                                    (const float*)(d + oUr), S, (const int32_t*)(d + oNodes), (const int32_t*)(d + oStarts), (const int32_t*)(d + oFeats),
                                                    (const int32_t*)(d + oMisc), d + oMp, dp, dp + 9, dp + 11, dp + 27, th_low, only_stereo, coarse, check_orientation,
                                                    (int32_t*)(d + oMatch), (int32_t*)(d + oNm), nullptr);
-    if (rc == ORBFE_OK && e == cudaSuccess) e = cudaDeviceSynchronize();
+    if (rc == ORBFE_OK && e == cudaSuccess) e = cudaStreamSynchronize(nullptr);   /* the launch above went to the default stream */
     if (rc == ORBFE_OK && e == cudaSuccess && n_1) e = cudaMemcpy(match_12, d + oMatch, (size_t)n_1 * 4, cudaMemcpyDeviceToHost);
     if (rc == ORBFE_OK && e == cudaSuccess && nmatches) e = cudaMemcpy(nmatches, d + oNm, 4, cudaMemcpyDeviceToHost);
     cudaFree(d);

@@ -245,8 +245,9 @@ int orbfe_clahe_apply(orbfe_clahe* c, const uint8_t* src, size_t sstep, uint8_t*
 int orbfe_clahe_lut(orbfe_clahe* c, int frame, uint8_t* out) {
     if (!c || !out || frame < 0 || frame >= c->maxBatch) { orbfe_set_error("bad argument"); return ORBFE_E_INVALID; }
     ORBFE_CUDA(cudaSetDevice(c->device));
-    ORBFE_CUDA(cudaDeviceSynchronize());
-    ORBFE_CUDA(cudaMemcpy(out, c->dLut + (size_t)frame * c->tilesX * c->tilesY * 256, (size_t)c->tilesX * c->tilesY * 256, cudaMemcpyDeviceToHost));
+    /* tables of the last apply call: on the object's stream unless the caller brought its own (then the caller has synchronised it) */
+    ORBFE_CUDA(cudaMemcpyAsync(out, c->dLut + (size_t)frame * c->tilesX * c->tilesY * 256, (size_t)c->tilesX * c->tilesY * 256, cudaMemcpyDeviceToHost, c->stream));
+    ORBFE_CUDA(cudaStreamSynchronize(c->stream));
     return ORBFE_OK;
 }
 

@@ -77,6 +77,15 @@ static int encode_tiled_u8_3d(CUtensorMap* out, void* base, uint64_t dim0, uint6
     return 0;
 }
 
+int orbfe_mark_last(orbfe_extractor* ex, cudaStream_t st) {
+    ORBFE_CUDA(cudaEventRecord(ex->evLast, st));
+    return 0;
+}
+int orbfe_wait_last(orbfe_extractor* ex) {
+    ORBFE_CUDA(cudaEventSynchronize(ex->evLast));
+    return 0;
+}
+
 template <typename T>
 static int dev_alloc(orbfe_extractor* ex, T** p, size_t count) {
     void* v = nullptr;
@@ -112,6 +121,7 @@ void orbfe_extractor_destroy(orbfe_extractor* ex) {
     for (cudaEvent_t ev : ex->evDone) if (ev) cudaEventDestroy(ev);
     for (cudaEvent_t ev : ex->evOut) if (ev) cudaEventDestroy(ev);
     for (cudaEvent_t ev : ex->evBatch) if (ev) cudaEventDestroy(ev);
+    if (ex->evLast) cudaEventDestroy(ex->evLast);
     if (ex->copyIn) cudaStreamDestroy(ex->copyIn);
     if (ex->copyOut) cudaStreamDestroy(ex->copyOut);
     if (ex->stream) cudaStreamDestroy(ex->stream);
@@ -354,6 +364,7 @@ int orbfe_extractor_create(const orbfe_params* p, int device, int width, int hei
     ex->evOutValid.assign(ex->evIn.size(), 0);
     for (cudaEvent_t& ev : ex->evOut) TRYC(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
     for (cudaEvent_t& ev : ex->evBatch) TRYC(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+    TRYC(cudaEventCreateWithFlags(&ex->evLast, cudaEventDisableTiming));
     for (cudaEvent_t& ev : ex->ev) TRYC(cudaEventCreate(&ev));
     TRY(dev_alloc(ex, &b.pyr, B * d.pyrSlab + 256));
     TRY(dev_alloc(ex, &b.blur, B * d.blurSlab + 256));
@@ -489,30 +500,35 @@ int orbfe_extract_batch_device(orbfe_extractor* ex, const uint8_t* d_images, int
     }
     ORBFE_CUDA(cudaSetDevice(ex->device));
     ex->lastBatch = nframes;
-    return orbfe_launch_extract(ex, d_images, nframes, lap0, lap1, stream ? (cudaStream_t)stream : ex->stream, 0);
+    cudaStream_t st = stream ? (cudaStream_t)stream : ex->stream;
+    const int rc = orbfe_launch_extract(ex, d_images, nframes, lap0, lap1, st, 0);
+    return rc ? rc : orbfe_mark_last(ex, st);
 }
 
 int orbfe_batch_counts(orbfe_extractor* ex, int nframes, int32_t* n, int32_t* mono) {
     if (!ex || nframes < 1 || nframes > ex->lastBatch) { orbfe_set_error("bad frame count"); return ORBFE_E_INVALID; }
     ORBFE_CUDA(cudaSetDevice(ex->device));
-    ORBFE_CUDA(cudaDeviceSynchronize());
-    if (n) ORBFE_CUDA(cudaMemcpy(n, ex->b.count, nframes * sizeof(int), cudaMemcpyDeviceToHost));
-    if (mono) ORBFE_CUDA(cudaMemcpy(mono, ex->b.mono, nframes * sizeof(int), cudaMemcpyDeviceToHost));
+    { const int rc = orbfe_wait_last(ex); if (rc) return rc; }
+    if (n) ORBFE_D2H(ex, n, ex->b.count, nframes * sizeof(int));
+    if (mono) ORBFE_D2H(ex, mono, ex->b.mono, nframes * sizeof(int));
+    ORBFE_D2H_DONE(ex);
     return ORBFE_OK;
 }
 
 int orbfe_batch_result(orbfe_extractor* ex, int frame, orbfe_keypoint* kps, uint8_t* desc, int cap, int* n, int* mono) {
     if (!ex || frame < 0 || frame >= ex->lastBatch) { orbfe_set_error("bad frame index"); return ORBFE_E_INVALID; }
     ORBFE_CUDA(cudaSetDevice(ex->device));
-    ORBFE_CUDA(cudaDeviceSynchronize());
+    { const int rc = orbfe_wait_last(ex); if (rc) return rc; }
     int cnt = 0, mi = 0;
-    ORBFE_CUDA(cudaMemcpy(&cnt, ex->b.count + frame, sizeof(int), cudaMemcpyDeviceToHost));
-    ORBFE_CUDA(cudaMemcpy(&mi, ex->b.mono + frame, sizeof(int), cudaMemcpyDeviceToHost));
+    ORBFE_D2H(ex, &cnt, ex->b.count + frame, sizeof(int));
+    ORBFE_D2H(ex, &mi, ex->b.mono + frame, sizeof(int));
+    ORBFE_D2H_DONE(ex);
     if (n) *n = cnt;
     if (mono) *mono = mi;
     if (cnt > cap) { orbfe_set_error("caller capacity %d < %d keypoints", cap, cnt); return ORBFE_E_CAPACITY; }
-    if (kps && cnt) ORBFE_CUDA(cudaMemcpy(kps, ex->b.kps + (size_t)frame * ex->d.kpCap, (size_t)cnt * sizeof(orbfe_keypoint), cudaMemcpyDeviceToHost));
-    if (desc && cnt) ORBFE_CUDA(cudaMemcpy(desc, ex->b.desc + (size_t)frame * ex->d.kpCap * 32, (size_t)cnt * 32, cudaMemcpyDeviceToHost));
+    if (kps && cnt) ORBFE_D2H(ex, kps, ex->b.kps + (size_t)frame * ex->d.kpCap, (size_t)cnt * sizeof(orbfe_keypoint));
+    if (desc && cnt) ORBFE_D2H(ex, desc, ex->b.desc + (size_t)frame * ex->d.kpCap * 32, (size_t)cnt * 32);
+    ORBFE_D2H_DONE(ex);
     return ORBFE_OK;
 }
 
@@ -766,40 +782,70 @@ int orbfe_extract(orbfe_extractor* ex, const uint8_t* image, int rows, int cols,
 int orbfe_pyramid_level(orbfe_extractor* ex, int frame, int level, int padded, uint8_t* dst) {
     if (!ex || !dst || level < 0 || level >= ex->d.nlevels || frame < 0 || frame >= ex->maxBatch) return ORBFE_E_INVALID;
     ORBFE_CUDA(cudaSetDevice(ex->device));
-    ORBFE_CUDA(cudaDeviceSynchronize());
+    { const int rc = orbfe_wait_last(ex); if (rc) return rc; }
     if (padded) {   /* the extraction writes only the 3 px of border it reads itself; the rest is filled here, once per batch */
         int rc = orbfe_materialize_borders(ex, ex->stream);
         if (rc) return rc;
-        ORBFE_CUDA(cudaStreamSynchronize(ex->stream));
     }
     const LevelDesc& L = ex->d.lv[level];
     const int B = padded ? ORBFE_EDGE : 0;
     const uint8_t* src = ex->b.pyr + (size_t)frame * ex->d.pyrSlab + L.pyrOff + (size_t)(ORBFE_EDGE - B) * L.pitch + ORBFE_ROW_LEAD - B;
-    ORBFE_CUDA(cudaMemcpy2D(dst, L.w + 2 * B, src, L.pitch, L.w + 2 * B, L.h + 2 * B, cudaMemcpyDeviceToHost));
+    ORBFE_D2H_2D(ex, dst, L.w + 2 * B, src, L.pitch, L.w + 2 * B, L.h + 2 * B);   /* stream order: behind the border kernel */
+    ORBFE_D2H_DONE(ex);
+    return ORBFE_OK;
+}
+
+int orbfe_pyramid_levels(orbfe_extractor* ex, int frame, int padded, uint8_t* const* dst_levels) {
+    if (!ex || !dst_levels || frame < 0 || frame >= ex->maxBatch) return ORBFE_E_INVALID;
+    ORBFE_CUDA(cudaSetDevice(ex->device));
+    { const int rc = orbfe_wait_last(ex); if (rc) return rc; }
+    if (padded) { const int rc = orbfe_materialize_borders(ex, ex->stream); if (rc) return rc; }
+    const int B = padded ? ORBFE_EDGE : 0;
+    for (int l = 0; l < ex->d.nlevels; l++) {
+        if (!dst_levels[l]) continue;
+        const LevelDesc& L = ex->d.lv[l];
+        const uint8_t* src = ex->b.pyr + (size_t)frame * ex->d.pyrSlab + L.pyrOff + (size_t)(ORBFE_EDGE - B) * L.pitch + ORBFE_ROW_LEAD - B;
+        ORBFE_D2H_2D(ex, dst_levels[l], L.w + 2 * B, src, L.pitch, L.w + 2 * B, L.h + 2 * B);
+    }
+    ORBFE_D2H_DONE(ex);   /* one wait for the border kernel and all the copies */
+    return ORBFE_OK;
+}
+
+int orbfe_pin_host(void* p, size_t bytes) {
+    if (!p || !bytes) return ORBFE_E_INVALID;
+    ORBFE_CUDA(cudaHostRegister(p, bytes, cudaHostRegisterDefault));
+    return ORBFE_OK;
+}
+
+int orbfe_unpin_host(void* p) {
+    if (!p) return ORBFE_E_INVALID;
+    ORBFE_CUDA(cudaHostUnregister(p));
     return ORBFE_OK;
 }
 
 int orbfe_blurred_level(orbfe_extractor* ex, int frame, int level, uint8_t* dst) {
     if (!ex || !dst || level < 0 || level >= ex->d.nlevels || frame < 0 || frame >= ex->maxBatch) return ORBFE_E_INVALID;
     ORBFE_CUDA(cudaSetDevice(ex->device));
-    ORBFE_CUDA(cudaDeviceSynchronize());
+    { const int rc = orbfe_wait_last(ex); if (rc) return rc; }
     const LevelDesc& L = ex->d.lv[level];
-    ORBFE_CUDA(cudaMemcpy2D(dst, L.w, ex->b.blur + (size_t)frame * ex->d.blurSlab + L.blurOff, L.bpitch, L.w, L.h, cudaMemcpyDeviceToHost));
+    ORBFE_D2H_2D(ex, dst, L.w, ex->b.blur + (size_t)frame * ex->d.blurSlab + L.blurOff, L.bpitch, L.w, L.h);
+    ORBFE_D2H_DONE(ex);
     return ORBFE_OK;
 }
 
 int orbfe_fast_candidates(orbfe_extractor* ex, int frame, int level, orbfe_keypoint* out, int cap, int* n) {
     if (!ex || level < 0 || level >= ex->d.nlevels || frame < 0 || frame >= ex->maxBatch) return ORBFE_E_INVALID;
     ORBFE_CUDA(cudaSetDevice(ex->device));
-    ORBFE_CUDA(cudaDeviceSynchronize());
+    { const int rc = orbfe_wait_last(ex); if (rc) return rc; }
     const LevelDesc& L = ex->d.lv[level];
     const int ncell = L.nCols * L.nRows;
     std::vector<int> counts(ncell);
     std::vector<CellDesc> cells(ncell);
-    ORBFE_CUDA(cudaMemcpy(counts.data(), ex->b.cellCount + (size_t)frame * ex->d.nCells + L.cellBase, ncell * sizeof(int), cudaMemcpyDeviceToHost));
-    ORBFE_CUDA(cudaMemcpy(cells.data(), ex->b.cells + L.cellBase, ncell * sizeof(CellDesc), cudaMemcpyDeviceToHost));
+    ORBFE_D2H(ex, counts.data(), ex->b.cellCount + (size_t)frame * ex->d.nCells + L.cellBase, ncell * sizeof(int));
+    ORBFE_D2H(ex, cells.data(), ex->b.cells + L.cellBase, ncell * sizeof(CellDesc));
     std::vector<uint32_t> keys(std::max(L.keyCap, 1));
-    ORBFE_CUDA(cudaMemcpy(keys.data(), ex->b.cand + (size_t)frame * ex->d.candCap + L.keyBase, (size_t)L.keyCap * 4, cudaMemcpyDeviceToHost));
+    ORBFE_D2H(ex, keys.data(), ex->b.cand + (size_t)frame * ex->d.candCap + L.keyBase, (size_t)L.keyCap * 4);
+    ORBFE_D2H_DONE(ex);
     int total = 0;
     for (int c = 0; c < ncell; c++)
         for (int i = 0; i < counts[c]; i++, total++) {

@@ -129,6 +129,7 @@ struct orbfe_extractor {
     std::vector<cudaEvent_t> evIn, evDone; /* one pair per chunk of hostChunk frames */
     std::vector<cudaEvent_t> evOut;        /* per chunk: the download of its results has finished (next batch may rewrite them) */
     std::vector<char> evOutValid;
+    cudaEvent_t evLast;                    /* recorded behind the last work enqueued for this object, on whichever stream took it */
     cudaEvent_t evBatch[2];                /* per submit slot: everything of that batch is on the host */
     uint8_t* inputStage2;                  /* second image staging buffer (slot 1 of orbfe_stereo_frames_submit), allocated on first use */
     int pendingHead, pendingCount, pendingFrames[2];
@@ -160,6 +161,14 @@ struct orbfe_extractor {
 ExBuffers orbfe_shift_frames(const ExBuffers& b, const ExDesc& d, int f0);
 /* Frame::ComputeStereoMatches kernels for frames [frame0, frame0 + nframes) of two extractors, enqueued on st */
 int orbfe_launch_stereo(orbfe_extractor* exL, orbfe_extractor* exR, int nframes, int frame0, float mbf, float minD, float maxD, cudaStream_t st);
+
+/* Getters wait for the object's own last work (not for the whole device: Tracking, LocalMapping and LoopClosing share the GPU)
+ * and copy on the object's stream. */
+int orbfe_mark_last(orbfe_extractor* ex, cudaStream_t st);
+int orbfe_wait_last(orbfe_extractor* ex);
+#define ORBFE_D2H(ex, dst, src, bytes) ORBFE_CUDA(cudaMemcpyAsync((dst), (src), (bytes), cudaMemcpyDeviceToHost, (ex)->stream))
+#define ORBFE_D2H_2D(ex, dst, dpitch, src, spitch, w, h) ORBFE_CUDA(cudaMemcpy2DAsync((dst), (dpitch), (src), (spitch), (w), (h), cudaMemcpyDeviceToHost, (ex)->stream))
+#define ORBFE_D2H_DONE(ex) ORBFE_CUDA(cudaStreamSynchronize((ex)->stream))
 
 void orbfe_set_error(const char* fmt, ...);
 int orbfe_cuda_fail(cudaError_t e, const char* what);

@@ -2,6 +2,7 @@
 // Built and run by tests/test_shim.py (GPU) / syntax-checked on CPU.
 #include <cstdio>
 #include <cstdlib>
+#include <string>
 #include <vector>
 #include "orbfe_shim/ORBextractor.h"     // replaces the reference's include/ORBextractor.h (same public surface)
 #include "orbfe_shim/orbfe_matching.h"   // next to the reference's own ORBmatcher.h / Frame.h, which stay as they are
@@ -35,8 +36,30 @@ int ORBmatcher::DescriptorDistance(const cv::Mat& a, const cv::Mat& b) { return 
 // src/Frame.cc:797-967
 void Frame::ComputeStereoMatches() { orbfe::ComputeStereoMatches(mpORBextractorLeft, mpORBextractorRight, N, mbf, mbf / mb, mvuRight, mvDepth); }
 }  // namespace ORB_SLAM3
+#include <chrono>
 int main(int argc, char** argv) {
     const int W = 752, H = 480;
+    if (argc > 2 && std::string(argv[1]) == "--latency") {
+        // single-frame latency of the drop-in as shipped: ORBextractor::operator() on a pageable host image, keypoints, descriptors and
+        // (unless built with -DORBFE_SHIM_LAZY_PYRAMID) the eight mvImagePyramid mirrors back on the host
+        const int iters = atoi(argv[2]);
+        cv::Mat im(H, W, CV_8UC1), im2(H, W, CV_8UC1), mask;
+        orbfe_synth_stereo(3, W, H, im.ptr<unsigned char>(0), im2.ptr<unsigned char>(0));
+        ORBextractor ex(1200, 1.2f, 8, 20, 7);
+        std::vector<cv::KeyPoint> k;
+        cv::Mat d;
+        std::vector<int> lap = {0, 0};
+        for (int i = 0; i < 10; i++) ex(im, mask, k, d, lap);
+        const auto t0 = std::chrono::steady_clock::now();
+        for (int i = 0; i < iters; i++) ex(i & 1 ? im2 : im, mask, k, d, lap);
+        const double us = std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - t0).count() / iters;
+#ifdef ORBFE_SHIM_LAZY_PYRAMID
+        printf("shim_latency_us=%.1f pyramid=lazy n=%zu\n", us, k.size());
+#else
+        printf("shim_latency_us=%.1f pyramid=mirrored n=%zu\n", us, k.size());
+#endif
+        return 0;
+    }
     cv::Mat imL(H, W, CV_8UC1), imR(H, W, CV_8UC1), mask;
     orbfe_synth_stereo(0, W, H, imL.ptr<unsigned char>(0), imR.ptr<unsigned char>(0));
     ORBextractor left(1200, 1.2f, 8, 20, 7), right(1200, 1.2f, 8, 20, 7);   // src/Tracking.cc:1151-1154
