@@ -221,6 +221,9 @@ int orbfe_nccl_comm_destroy(void* comm);
  * keep them on one stream or otherwise ordered. */
 int orbfe_hamming_top2_static(int device, const uint8_t* d_queries, int nq, const uint8_t* d_db, int64_t ndb,
                               int64_t index_base, int th, float ratio, int strict_lt, orbfe_match* d_out, void* stream);
+/* Measures the device's POPC issue rate (32-bit population counts per second, whole GPU) with a small kernel; bench.py reads
+ * the Hamming search's integer-pipe roofline against it.  No counterpart in the reference. */
+int orbfe_probe_popc(int device, double* popc_per_second);
 /* One-shot convenience over host memory (creates and destroys a matcher). */
 int orbfe_hamming_top2(int device, const uint8_t* q, int nq, const uint8_t* db, int64_t ndb, int th, float ratio,
                        int strict_lt, orbfe_match* out);
@@ -229,6 +232,14 @@ int orbfe_hamming_top2(int device, const uint8_t* q, int nq, const uint8_t* db, 
  * Frame::ComputeStereoFishEyeMatches (src/Frame.cc:1137-1144).  match[i] = train row or -1; d0/d1 optional. */
 int orbfe_knn2_ratio(int device, const uint8_t* q, int nq, const uint8_t* t, int nt, double ratio, int32_t* match,
                      int32_t* d0, int32_t* d1);
+
+/* The same matching step for a batch of fisheye stereo frames that the two extractors have just processed (device resident,
+ * vLappingArea given to both): queries = the left keypoints inside the lapping area (rows mono_l .. n_l-1 of each frame, where
+ * operator() placed them, src/ORBextractor.cc:1135-1139), train rows = the right ones; d_match_lr[f*cap + row] = matched right row
+ * (index into the right frame's keypoints, i.e. trainIdx + monoRight as in src/Frame.cc:1151) or -1, cap = keypoint capacity;
+ * d_dist01 (optional, [nframes*cap][2]) receives the two smallest distances.  Asynchronous on `stream`. */
+int orbfe_fisheye_match_batch_device(orbfe_extractor* exL, orbfe_extractor* exR, int nframes, double ratio, int32_t* d_match_lr, int32_t* d_dist01,
+                                     void* stream);
 
 /* ------------------------------------------------------------------------------------ bag-of-words assignment (N2) */
 /* Replaces Frame::ComputeBoW / KeyFrame::ComputeBoW (src/Frame.cc:724-731, src/KeyFrame.cc:105-114):

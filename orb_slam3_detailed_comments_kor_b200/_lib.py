@@ -56,6 +56,8 @@ SIGNATURES = {
     "orbfe_batch_device_views": (i32, [vp, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]),
     "orbfe_pyramid_level": (i32, [vp, i32, i32, i32, vp]),
     "orbfe_pyramid_levels": (i32, [vp, i32, i32, vp]),
+    "orbfe_probe_popc": (i32, [i32, C.POINTER(C.c_double)]),
+    "orbfe_fisheye_match_batch_device": (i32, [vp, vp, i32, C.c_double, vp, vp, vp]),
     "orbfe_pin_host": (i32, [vp, sz]),
     "orbfe_unpin_host": (i32, [vp]),
     "orbfe_blurred_level": (i32, [vp, i32, i32, vp]),

@@ -18,6 +18,7 @@
 #include <new>
 
 #include "orbfe_internal.h"
+#include "orbfe_tma.cuh"
 
 int orbfe_collect_stage_times(orbfe_extractor* ex);
 
@@ -39,16 +40,9 @@ static __device__ __forceinline__ int ham256(const uint32_t (&q)[8], const uint4
     return __popc(s0) + __popc(s1) + __popc(x6) + __popc(x7) + 2 * (__popc(c0) + __popc(c1));
 }
 
-static __device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
-    const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(s), "l"(gmem));
-}
-static __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::); }
-template <int N>
-static __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N)); }
 
 /* grid = (query tiles, database slices).  Each thread keeps T2_QPT queries in registers and scans its CTA's
- * slice, streamed through a double-buffered cp.async stage that the whole CTA reads by broadcast.
+ * slice, streamed through a double-buffered bulk-copy (TMA) stage that the whole CTA reads by broadcast.
  * Scan order inside a thread is ascending row, so strict `<` keeps the lowest row on ties, exactly like the
  * reference's sequential loop.  Output: one orbfe_match per (slice, query) in `parts` (idx is global). */
 __global__ void __launch_bounds__(T2_NT) k_top2_partial(const uint4* __restrict__ q, int nq, const uint4* __restrict__ db,
@@ -71,18 +65,22 @@ __global__ void __launch_bounds__(T2_NT) k_top2_partial(const uint4* __restrict_
     }
     const uint4* src = db + 2 * r0;
     const int nchunks = (nrows + T2_CHUNK - 1) / T2_CHUNK;
+    /* the slice arrives as linear bulk copies (cp.async.bulk: one instruction per 8 KB stage, issued by one thread, completion on
+     * an mbarrier per buffer) instead of one 16-byte cp.async per thread */
+    __shared__ __align__(8) uint64_t s_bar[2];
+    if (threadIdx.x == 0) { mbar_init(&s_bar[0], 1); mbar_init(&s_bar[1], 1); }
+    __syncthreads();
     auto stage = [&](int c, int buf) {
-        const int base = c * T2_CHUNK * 2;               /* uint4 index inside the slice */
-        const int lim = nrows * 2;
-        for (int i = threadIdx.x; i < T2_CHUNK * 2; i += T2_NT)
-            if (base + i < lim) cp_async16(&s_db[buf][i], src + base + i);
-        cp_async_commit();
+        if (threadIdx.x == 0) {
+            const uint32_t bytes = (uint32_t)min(T2_CHUNK, nrows - c * T2_CHUNK) * 32u;
+            mbar_expect_tx(&s_bar[buf], bytes);
+            bulk_load(&s_db[buf][0], src + (size_t)c * T2_CHUNK * 2, bytes, &s_bar[buf]);
+        }
     };
     if (nchunks > 0) stage(0, 0);
     for (int c = 0; c < nchunks; c++) {
-        if (c + 1 < nchunks) { stage(c + 1, (c + 1) & 1); cp_async_wait<1>(); }
-        else cp_async_wait<0>();
-        __syncthreads();
+        if (c + 1 < nchunks) stage(c + 1, (c + 1) & 1);   /* its buffer was released by the barrier that ended iteration c-1 */
+        mbar_wait(&s_bar[c & 1], (uint32_t)(c >> 1) & 1u);
         const uint4* s = s_db[c & 1];
         const int rows = min(T2_CHUNK, nrows - c * T2_CHUNK);
         const int rowBase = (int)(indexBase + r0) + c * T2_CHUNK;
@@ -131,6 +129,66 @@ __global__ void k_top2_merge(const orbfe_match* __restrict__ parts, int nshards,
     orbfe_match r;
     r.best1 = b1; r.best2 = b2; r.idx = bi; r.accepted = ok;
     out[qi] = r;
+}
+
+/* Matching step of Frame::ComputeStereoFishEyeMatches (src/Frame.cc:1119-1144) for a batch of frames straight from the two
+ * extractors' device buffers: the queries of frame f are the left keypoints inside the lapping area (rows monoL .. nL-1, where
+ * ORBextractor::operator() put them), the train rows the right ones (monoR .. nR-1); BFMatcher(NORM_HAMMING).knnMatch(k=2) keeps
+ * the two smallest distances with ties to the lowest train row, and the match survives iff there are two rows and
+ * d0 < d1*ratio with the float distances promoted to double by the 0.7 literal.  One thread = one query, a CTA's 256 queries
+ * share the train rows, which stream through shared memory as bulk copies.  match_lr[f*cap + row] = right row or -1. */
+#define KB_NT 256
+__global__ void __launch_bounds__(KB_NT) k_fisheye_knn2(const __grid_constant__ ExDesc d, ExBuffers Lb, ExBuffers Rb, double ratio, int32_t* __restrict__ matchLR,
+                                                        int32_t* __restrict__ dist01) {
+    __shared__ __align__(16) uint4 s_db[2][T2_CHUNK * 2];
+    __shared__ __align__(8) uint64_t s_bar[2];
+    const size_t f = blockIdx.y;
+    const int nL = Lb.count[f], monoL = Lb.mono[f], nR = Rb.count[f], monoR = Rb.mono[f];
+    const int nq = nL - monoL, nt = nR - monoR;
+    int32_t* out = matchLR + f * d.kpCap;
+    if (blockIdx.x == 0)
+        for (int i = threadIdx.x; i < monoL; i += KB_NT) out[i] = -1;     /* outside the lapping area: never matched */
+    if ((int)blockIdx.x * KB_NT >= nq) return;
+    if (threadIdx.x == 0) { mbar_init(&s_bar[0], 1); mbar_init(&s_bar[1], 1); }
+    __syncthreads();
+    const int qi = blockIdx.x * KB_NT + threadIdx.x;
+    uint32_t qr[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    if (qi < nq) {
+        const uint4* q = reinterpret_cast<const uint4*>(Lb.desc + (f * d.kpCap + monoL + qi) * 32);
+        const uint4 a = __ldg(q), b = __ldg(q + 1);
+        qr[0] = a.x; qr[1] = a.y; qr[2] = a.z; qr[3] = a.w; qr[4] = b.x; qr[5] = b.y; qr[6] = b.z; qr[7] = b.w;
+    }
+    const uint4* src = reinterpret_cast<const uint4*>(Rb.desc + (f * d.kpCap + monoR) * 32);
+    const int nchunks = (nt + T2_CHUNK - 1) / T2_CHUNK;
+    auto stage = [&](int c, int buf) {
+        if (threadIdx.x == 0) {
+            const uint32_t bytes = (uint32_t)min(T2_CHUNK, nt - c * T2_CHUNK) * 32u;
+            mbar_expect_tx(&s_bar[buf], bytes);
+            bulk_load(&s_db[buf][0], src + (size_t)c * T2_CHUNK * 2, bytes, &s_bar[buf]);
+        }
+    };
+    int b1 = 257, b2 = 257, bi = -1;
+    if (nchunks > 0) stage(0, 0);
+    for (int c = 0; c < nchunks; c++) {
+        if (c + 1 < nchunks) stage(c + 1, (c + 1) & 1);
+        mbar_wait(&s_bar[c & 1], (uint32_t)(c >> 1) & 1u);
+        const uint4* s = s_db[c & 1];
+        const int rows = min(T2_CHUNK, nt - c * T2_CHUNK);
+#pragma unroll 4
+        for (int r = 0; r < rows; r++) {
+            const int dist = ham256(qr, s[2 * r], s[2 * r + 1]);
+            if (dist < b2) {
+                if (dist < b1) { b2 = b1; b1 = dist; bi = c * T2_CHUNK + r; }
+                else b2 = dist;
+            }
+        }
+        __syncthreads();
+    }
+    if (qi < nq) {
+        const bool ok = nt >= 2 && ((double)(float)b1 < (double)(float)b2 * ratio);
+        out[monoL + qi] = ok ? monoR + bi : -1;
+        if (dist01) { dist01[2 * (f * d.kpCap + monoL + qi)] = b1; dist01[2 * (f * d.kpCap + monoL + qi) + 1] = b2; }
+    }
 }
 
 __global__ void k_pair_distances(const uint4* __restrict__ a, const uint4* __restrict__ b, long long n, int* __restrict__ out) {
@@ -454,6 +512,19 @@ int orbfe_stereo_match_batch_device(orbfe_extractor* exL, orbfe_extractor* exR, 
         ORBFE_CUDA(cudaEventRecord(ev[1], st));
         exL->stereoPending = 1;
     }
+    { int rc = orbfe_mark_last(exL, st); if (!rc) rc = orbfe_mark_last(exR, st); if (rc) return rc; }
+    return ORBFE_OK;
+}
+
+int orbfe_fisheye_match_batch_device(orbfe_extractor* exL, orbfe_extractor* exR, int nframes, double ratio, int32_t* d_match_lr, int32_t* d_dist01, void* stream) {
+    if (!exL || !exR || !d_match_lr) { orbfe_set_error("null argument"); return ORBFE_E_INVALID; }
+    if (!same_geometry(exL, exR)) { orbfe_set_error("left/right extractors differ in geometry or device"); return ORBFE_E_INVALID; }
+    if (nframes < 1 || nframes > exL->lastBatch || nframes > exR->lastBatch) { orbfe_set_error("nframes exceeds the last extracted batch"); return ORBFE_E_INVALID; }
+    ORBFE_CUDA(cudaSetDevice(exL->device));
+    cudaStream_t st = stream ? (cudaStream_t)stream : exL->stream;
+    if (!stream) ORBFE_CUDA(cudaStreamSynchronize(exR->stream)); /* right extraction ran on its own stream */
+    k_fisheye_knn2<<<dim3((exL->d.kpCap + KB_NT - 1) / KB_NT, nframes), KB_NT, 0, st>>>(exL->d, exL->b, exR->b, ratio, d_match_lr, d_dist01);
+    ORBFE_CUDA(cudaGetLastError());
     { int rc = orbfe_mark_last(exL, st); if (!rc) rc = orbfe_mark_last(exR, st); if (rc) return rc; }
     return ORBFE_OK;
 }
@@ -789,6 +860,49 @@ int orbfe_distinctive_descriptors(int device, const uint8_t* desc, const int32_t
 }
 
 }  /* extern "C" */
+
+/* ------------------------------------------------------------------------------------- POPC throughput probe */
+/* What the integer roofline of the Hamming search is read against (SURVEY.md 8d asks for a measured figure, not the nominal
+ * 16 POPC/clk/SM): every thread runs eight independent POPC chains; the adds that keep the chains alive go to the ALU pipe. */
+__global__ void __launch_bounds__(256) k_probe_popc(uint32_t* sink, int iters) {
+    uint32_t x[8], acc[8];
+#pragma unroll
+    for (int j = 0; j < 8; j++) { x[j] = (threadIdx.x + 1u) * 2654435761u + j * 40503u + blockIdx.x; acc[j] = 0; }
+    for (int it = 0; it < iters; it++) {
+#pragma unroll
+        for (int j = 0; j < 8; j++) { acc[j] += __popc(x[j]); x[j] += acc[j]; }
+    }
+    uint32_t t = 0;
+#pragma unroll
+    for (int j = 0; j < 8; j++) t ^= acc[j] + x[j];
+    if (t == 0x12345678u) sink[0] = t;   /* never true in practice; keeps the chains from being removed */
+}
+
+extern "C" int orbfe_probe_popc(int device, double* popc_per_second) {
+    if (!popc_per_second) { orbfe_set_error("bad argument"); return ORBFE_E_INVALID; }
+    ORBFE_CUDA(cudaSetDevice(device));
+    uint32_t* sink = nullptr;
+    ORBFE_CUDA(cudaMalloc((void**)&sink, 4));
+    cudaEvent_t e0, e1;
+    ORBFE_CUDA(cudaEventCreate(&e0));
+    ORBFE_CUDA(cudaEventCreate(&e1));
+    const int iters = 4096, blocks = 148 * 8;
+    k_probe_popc<<<blocks, 256>>>(sink, iters);   /* warm-up */
+    double best = 0.0;
+    for (int rep = 0; rep < 5; rep++) {
+        cudaEventRecord(e0);
+        k_probe_popc<<<blocks, 256>>>(sink, iters);
+        cudaEventRecord(e1);
+        cudaError_t e = cudaEventSynchronize(e1);
+        float ms = 0.f;
+        if (e == cudaSuccess) e = cudaEventElapsedTime(&ms, e0, e1);
+        if (e != cudaSuccess) { cudaFree(sink); return orbfe_cuda_fail(e, "popc probe"); }
+        best = std::max(best, (double)blocks * 256.0 * iters * 8.0 / (ms * 1e-3));
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(sink);
+    *popc_per_second = best;
+    return ORBFE_OK;
+}
 
 /* ------------------------------------------------------------------------- top-2 search without any allocation */
 /* orbfe_hamming_top2_static: the same top-2 search as orbfe_matcher_top2_device for callers that must not, or

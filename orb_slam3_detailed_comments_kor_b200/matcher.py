@@ -130,6 +130,12 @@ def stereo_frames_wait(exL, exR, out):
     return out
 
 
+def fisheye_match_batch_device(exL, exR, nframes, ratio, d_match_lr, d_dist01=None, stream=None):
+    """Matching step of Frame::ComputeStereoFishEyeMatches (src/Frame.cc:1119-1144) for the frames exL / exR extracted last."""
+    check(_lib.lib().orbfe_fisheye_match_batch_device(exL.handle, exR.handle, nframes, float(ratio), C.c_void_p(d_match_lr),
+                                                      C.c_void_p(d_dist01) if d_dist01 else None, C.c_void_p(stream) if stream else None))
+
+
 def stereo_result(exL, frame):
     u = np.zeros(exL.capacity, np.float32)
     d = np.zeros(exL.capacity, np.float32)

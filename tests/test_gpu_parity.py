@@ -573,6 +573,45 @@ def test_knn2_matches_oracle_and_golden(name):
     exL.close(); exR.close()
 
 
+def test_fisheye_match_batch_on_device():
+    """orbfe_fisheye_match_batch_device: ComputeStereoFishEyeMatches' knn-2 + 0.7 ratio step (src/Frame.cc:1119-1144) for a batch of
+    TUM-VI-shaped pairs straight from the extractors' device buffers, against the oracle's knn-2 on the downloaded descriptors.
+    One lapping interval puts every keypoint in the stereo part (mono = 0), the other splits the frame; one pair has a blank
+    right image (no train rows), one a blank left image (no queries)."""
+    import torch
+    W, H, params, nb = 512, 512, (1500, 1.2, 8, 20, 7), 5
+    pairs = [synth.stereo_pair(700 + i, W, H) for i in range(nb)]
+    Ls = np.stack([p[0] for p in pairs]); Rs = np.stack([p[1] for p in pairs])
+    Rs[3] = 90; Ls[4] = 17
+    exL = ORBextractor(*params, width=W, height=H, max_batch=nb)
+    exR = ORBextractor(*params, width=W, height=H, max_batch=nb)
+    cap = exL.capacity
+    grand = []
+    for lap in [(0, 511), (150, 400)]:
+        cl, ml, kl, dl = [a.copy() for a in exL.extract_batch_host(Ls, lap)]
+        cr, mr, kr, dr = [a.copy() for a in exR.extract_batch_host(Rs, lap)]
+        d_match = torch.full((nb, cap), -7, dtype=torch.int32, device="cuda")
+        d_dist = torch.zeros((nb, cap, 2), dtype=torch.int32, device="cuda")
+        M.fisheye_match_batch_device(exL, exR, nb, 0.7, d_match.data_ptr(), d_dist.data_ptr())
+        torch.cuda.synchronize()
+        got, gd = d_match.cpu().numpy(), d_dist.cpu().numpy()
+        total = 0
+        for f in range(nb):
+            q, t = dl[f, ml[f]:cl[f]], dr[f, mr[f]:cr[f]]
+            want = np.full(cl[f], -1, np.int32)
+            if len(q):
+                m, d0, d1 = O.knn2_ratio(q, t, 0.7) if len(t) else (np.full(len(q), -1, np.int32), None, None)
+                want[ml[f]:] = np.where(m >= 0, m + mr[f], -1)
+                if len(t) >= 2:
+                    assert np.array_equal(gd[f, ml[f]:cl[f], 0], d0) and np.array_equal(gd[f, ml[f]:cl[f], 1], d1), "distances frame %d" % f
+            assert np.array_equal(got[f, :cl[f]], want), "frame %d lap %s" % (f, lap)
+            total += int((want >= 0).sum())
+        grand.append(total)
+        assert cr[3] == 0 and cl[4] == 0 and (got[3, :cl[3]] == -1).all()
+    assert grand[0] > 20 and grand[1] > 0, grand       # knn-2 over whole frames with the 0.7 ratio keeps few, but not no, pairs
+    exL.close(); exR.close()
+
+
 def test_knn2_degenerate_train_sizes():
     q = np.random.RandomState(1).randint(0, 256, (5, 32)).astype(np.uint8)
     m, d0, d1 = M.knn2_ratio(q, q[:1], 0.7)            # one train row: knnMatch returns <2 -> rejected (Frame.cc:1144)
