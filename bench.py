@@ -31,6 +31,25 @@ PARAMS = (1200, 1.2, 8, 20, 7)
 MBF, FX = 47.90639, 435.2047             # Examples/Stereo-Inertial/EuRoC.yaml:9,26
 WORKLOAD = "euroc_stereo_2x752x480_1200feat_extract+ComputeStereoMatches"
 METRIC = "orb_frames_per_sec_752x480_1200feat"
+LAP = (0, 0)
+# BASELINE.json configs: [1] EuRoC (the headline, default), [2] TUM-VI fisheye stereo, [3] KITTI x 4096 images sharded by frame
+WORKLOADS = {
+    "euroc": dict(W=752, H=480, params=(1200, 1.2, 8, 20, 7), mbf=47.90639, fx=435.2047, lap=(0, 0), match="stereo", scaling="weak",
+                  name="euroc_stereo_2x752x480_1200feat_extract+ComputeStereoMatches", metric="orb_frames_per_sec_752x480_1200feat"),
+    # Examples/Stereo/KITTI00-02.yaml:9,21-22,28,41; 4096 images = 2048 pairs in total, split over the ranks (strong scaling)
+    "kitti": dict(W=1241, H=376, params=(2000, 1.2, 8, 20, 7), mbf=386.1448, fx=718.856, lap=(0, 0), match="stereo", scaling="strong", total_pairs=2048,
+                  name="kitti_stereo_1241x376_2000feat_4096_images_extract+ComputeStereoMatches", metric="orb_frames_per_sec_1241x376_2000feat"),
+    # Examples/Stereo-Inertial/TUM_512.yaml:42-46 (lapping 0..511 on both cameras), knn-2 + 0.7 of ComputeStereoFishEyeMatches
+    "tumvi": dict(W=512, H=512, params=(1500, 1.2, 8, 20, 7), mbf=0.0, fx=0.0, lap=(0, 511), match="fisheye", scaling="weak",
+                  name="tumvi_fisheye_stereo_2x512x512_1500feat_lapping_extract+knn2_ratio", metric="orb_frames_per_sec_512x512_1500feat"),
+}
+
+
+def set_workload(name):
+    global W, H, PARAMS, MBF, FX, WORKLOAD, METRIC, LAP
+    w = WORKLOADS[name]
+    W, H, PARAMS, MBF, FX, WORKLOAD, METRIC, LAP = w["W"], w["H"], w["params"], w["mbf"], w["fx"], w["name"], w["metric"], w["lap"]
+    return w
 STAGES = ["pyramid", "fast", "blur", "quadtree", "assemble", "orient_describe", "stereo", "stereo_median"]
 
 
@@ -55,14 +74,18 @@ def algorithmic_bytes(nkp):
     return per, sum(per.values())
 
 
-def gen_pairs(n, seed0, pin):
+def gen_pairs(n, seed0, pin, distinct=None):
+    """n synthetic stereo pairs in (pinned) host tensors; with `distinct` < n only that many are generated and then repeated."""
     import torch
     from orb_slam3_detailed_comments_kor_b200 import synth
     tl = torch.empty((n, H, W), dtype=torch.uint8, pin_memory=pin)
     tr = torch.empty((n, H, W), dtype=torch.uint8, pin_memory=pin)
     L, R = tl.numpy(), tr.numpy()
+    nd = n if distinct is None else min(n, distinct)
     with ThreadPoolExecutor(os.cpu_count() or 4) as ex:
-        list(ex.map(lambda i: synth.stereo_pair(seed0 + i, W, H, L[i], R[i]), range(n)))
+        list(ex.map(lambda i: synth.stereo_pair(seed0 + i, W, H, L[i], R[i]), range(nd)))
+    for i in range(nd, n):
+        L[i] = L[i % nd]; R[i] = R[i % nd]
     return tl, tr
 
 
@@ -141,21 +164,56 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm), "source": "nvidia-smi"}
 
 
-def cpu_oracle_rate(npairs, threads):
-    """The CPU oracle (oracle/liborb_oracle.so) on `npairs` stereo pairs with `threads` host threads, timed the way the
-    reference instruments itself (around extraction and ComputeStereoMatches, src/Frame.cc:116-127,136-144)."""
+def reference_available():
+    """oracle/_ref/liborb_ref.so: the reference's own ORBextractor.cc + Frame::ComputeStereoMatches compiled by oracle/Makefile
+    (prebuilt where /root/reference exists; it travels to the GPU box with the repository snapshot)."""
+    try:
+        from oracle import ref_oracle as Rf
+        return Rf.available()
+    except Exception:
+        return False
+
+
+def cpu_oracle_rate(npairs, threads, impl="auto"):
+    """The reference's CPU path on `npairs` stereo pairs with `threads` host threads, timed the way the reference instruments
+    itself (around extraction and ComputeStereoMatches, src/Frame.cc:116-127,136-144).  impl "reference" = the reference's own code
+    (oracle/_ref), "port" = the CPU oracle restatement (oracle/liborb_oracle.so); "auto" takes the reference when it is there."""
     from oracle import orb_oracle as O
     from orb_slam3_detailed_comments_kor_b200 import synth
     pairs = [synth.stereo_pair(900000 + i, W, H) for i in range(npairs)]
     local = threading.local()
+    if impl == "auto":
+        impl = "reference" if reference_available() else "port"
+    if impl == "reference":
+        from oracle import ref_oracle as Rf
+        ref = Rf.ReferenceExtractor(*PARAMS)
+        mb = float(np.float32(MBF) / np.float32(FX)) if FX > 0 else 0.0
+
+        def work(i):   # noqa: F811
+            if FX > 0:   # both extractions + Frame::ComputeStereoMatches in the reference's code
+                return len(ref.stereo(pairs[i][0], pairs[i][1], MBF, mb)[0])
+            mL, kL, dL = ref(pairs[i][0], LAP)
+            mR, kR, dR = ref(pairs[i][1], LAP)
+            if len(kL) > mL and len(kR) > mR:
+                O.knn2_ratio(dL[mL:], dR[mR:], 0.7)          # BFMatcher.knnMatch is OpenCV code: the oracle's restatement stands in
+            return len(kL)
+        with ThreadPoolExecutor(threads) as ex:
+            list(ex.map(work, range(min(threads, npairs))))
+            t0 = time.perf_counter()
+            list(ex.map(work, range(npairs)))
+            dt = time.perf_counter() - t0
+        return 2 * npairs / dt, dt
 
     def work(i):
         if not hasattr(local, "ex"):
             local.ex = (O.OracleExtractor(*PARAMS), O.OracleExtractor(*PARAMS))
         exL, exR = local.ex
-        _, kL, dL = exL(pairs[i][0])
-        _, kR, dR = exR(pairs[i][1])
-        O.stereo_match(exL, exR, kL, dL, kR, dR, MBF, 0.0, FX)
+        mL, kL, dL = exL(pairs[i][0], LAP)
+        mR, kR, dR = exR(pairs[i][1], LAP)
+        if FX > 0:
+            O.stereo_match(exL, exR, kL, dL, kR, dR, MBF, 0.0, FX)
+        elif len(kL) > mL and len(kR) > mR:
+            O.knn2_ratio(dL[mL:], dR[mR:], 0.7)              # ComputeStereoFishEyeMatches' matching step, src/Frame.cc:1137-1144
         return len(kL)
 
     with ThreadPoolExecutor(threads) as ex:
@@ -164,6 +222,77 @@ def cpu_oracle_rate(npairs, threads):
         list(ex.map(work, range(npairs)))
         dt = time.perf_counter() - t0
     return 2 * npairs / dt, dt
+
+
+def cv2_lines(nframes, threads):
+    """Two more CPU figures with the real OpenCV (the cv2 wheel: SIMD FAST / GaussianBlur / resize, as a real ORB-SLAM3 binary has):
+    `cv2_primitives_frames_per_s` = only the pixel primitives of one extraction (pyramid resize + border, FAST per 35 px cell with the
+    20/7 retry, 7x7 blur of every level; frame-parallel over `threads`, one OpenCV thread each), called through cv2's Python binding — its
+    700 detect() calls per frame each build a Python list of KeyPoint objects, so binding overhead is part of the figure;
+    `cv2_frames_per_s` = tools/make_goldens.py::CvExtractor, the same primitives with the glue in Python (one thread: the glue holds
+    the interpreter lock).  Neither is a C++ OpenCV build of the reference (its headers are not in this image); they are the closest
+    thing to "real OpenCV arithmetic, timed" that the box can run."""
+    try:
+        import cv2
+        sys.path.insert(0, os.path.join(ROOT, "tools"))
+        import make_goldens as G
+    except Exception as exc:
+        return {"cv2": "unavailable: %r" % (exc,)}
+    from orb_slam3_detailed_comments_kor_b200 import synth
+    cv2.setNumThreads(1)
+    imgs = [synth.frame(910000 + i, W, H) for i in range(nframes)]
+    local = threading.local()
+
+    def primitives(i):
+        if not hasattr(local, "ex"):
+            local.ex = G.CvExtractor(*PARAMS)
+        ex = local.ex
+        ex.compute_pyramid(imgs[i])
+        ncorner = 0
+        for l in range(ex.nlevels):
+            im = ex.pyr[l]
+            minB, maxBX, maxBY = 16, im.shape[1] - 16, im.shape[0] - 16
+            width, height = np.float32(maxBX - minB), np.float32(maxBY - minB)
+            nCols, nRows = int(width / np.float32(35)), int(height / np.float32(35))
+            wCell, hCell = int(np.ceil(float(width / np.float32(nCols)))), int(np.ceil(float(height / np.float32(nRows))))
+            for ci in range(nRows):
+                iniY = minB + ci * hCell
+                if iniY >= maxBY - 3:
+                    continue
+                maxY = min(iniY + hCell + 6, maxBY)
+                for cj in range(nCols):
+                    iniX = minB + cj * wCell
+                    if iniX >= maxBX - 6:
+                        continue
+                    roi = im[iniY:maxY, iniX:min(iniX + wCell + 6, maxBX)]
+                    kps = ex.fast[ex.ini_th].detect(roi)
+                    if not kps:
+                        kps = ex.fast[ex.min_th].detect(roi)
+                    ncorner += len(kps)
+            cv2.GaussianBlur(im.copy(), (7, 7), 2, sigmaY=2, borderType=cv2.BORDER_REFLECT_101)
+        return ncorner
+
+    with ThreadPoolExecutor(threads) as tp:
+        list(tp.map(primitives, range(min(threads, nframes))))
+        t0 = time.perf_counter()
+        list(tp.map(primitives, range(nframes)))
+        dt = time.perf_counter() - t0
+    full = G.CvExtractor(*PARAMS)
+    nfull = min(4, nframes)
+    t0 = time.perf_counter()
+    for i in range(nfull):
+        full(imgs[i], LAP)
+    dtf = time.perf_counter() - t0
+    return {"cv2_version": cv2.__version__, "cv2_primitives_frames_per_s": nframes / dt,
+            "cv2_primitives_sample": "%d frames (%.1f s wall), frame-parallel over %d threads, cv2.setNumThreads(1)" % (nframes, dt, threads),
+            "cv2_frames_per_s": nfull / dtf, "cv2_sample": "%d frames (%.1f s wall), one thread, Python glue" % (nfull, dtf)}
+
+
+def peaks_for_issue():
+    try:
+        return float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))).get("sm_max_mhz", 1965.0))
+    except (OSError, ValueError):
+        return 1965.0
 
 
 def cpu_hamming_rate(nq_sample, ndb, threads):
@@ -185,12 +314,15 @@ def run_reference(args, rank):
         return
     cores = os.cpu_count() or 1
     sample = max(4, 4 * cores)
+    kind = "reference" if reference_available() else "port"
     for _ in range(args.warmup):
-        cpu_oracle_rate(min(sample, cores), cores)
+        cpu_oracle_rate(min(sample, cores), cores, kind)
     times = []
     for _ in range(args.steps):
-        _, dt = cpu_oracle_rate(sample, cores)
+        _, dt = cpu_oracle_rate(sample, cores, kind)
         times.append(dt)
+    port_rate, _ = cpu_oracle_rate(sample, cores, "port")
+    extra = cv2_lines(2 * cores, cores)
     ms = 1e3 * float(np.mean(times))
     value = 2 * sample / (ms / 1e3)
     hq = 1024
@@ -199,12 +331,167 @@ def run_reference(args, rank):
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "u8", "data": "synthetic",
             "config": {"workload": WORKLOAD, "pairs_per_step": sample, "threads": cores},
-            "cpu_baseline": {"value": value, "unit": "frames/s", "cores": cores, "kind": "port",
-                             "sample": "%d stereo pairs per step, frame-parallel over %d threads" % (sample, cores)},
+            "cpu_baseline": dict({"value": value, "unit": "frames/s", "cores": cores, "kind": kind,
+                                  "sample": "%d stereo pairs per step, frame-parallel over %d threads; %s" % (
+                                      sample, cores, "the reference's ORBextractor.cc + Frame::ComputeStereoMatches compiled by oracle/Makefile (OpenCV primitives: "
+                                      "scalar restatements pinned to cv2 4.13)" if kind == "reference" else "CPU oracle restatement"),
+                                  "port_frames_per_s": port_rate}, **extra),
             "e2e": {"value": value, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "hamming": {"value": hv, "unit": "descriptor_pairs/s", "sample": "%d queries x 2^20 rows (%.1f s wall)" % (hq, hdt),
                         "cores": cores}}
     print(json.dumps(line), flush=True)
+
+
+def run_workload(args, wl, rank, world, local_rank, barrier, max_over_ranks):
+    """BASELINE.json configs 3 (TUM-VI) and 4 (KITTI x 4096 images): the same measurement as the headline config — device-resident
+    throughput with CUDA events, per-stage times, roofline of the longest stage, end-to-end from pinned host memory, CPU sample —
+    on the workload's own shape, features and matching step.  A step = every pair of this rank once, in sub-batches of at most 256
+    pairs (the extractor objects' batch size); kitti splits 2048 pairs over the ranks (strong scaling), tumvi gives every rank its
+    own 256 pairs (weak)."""
+    import ctypes as C
+    import torch
+    from orb_slam3_detailed_comments_kor_b200 import ORBextractor, _lib
+    from orb_slam3_detailed_comments_kor_b200 import matcher as M
+    L = _lib.lib()
+    P = wl["total_pairs"] // world if wl["scaling"] == "strong" else args.pairs
+    SUB = min(P, 256)
+    assert P % SUB == 0
+    fisheye = wl["match"] == "fisheye"
+    hL, hR = gen_pairs(P, rank * 1000003, pin=True, distinct=64)
+    dL, dR = hL.cuda(non_blocking=True), hR.cuda(non_blocking=True)
+    exL = ORBextractor(*PARAMS, width=W, height=H, device=local_rank, max_batch=SUB)
+    exR = ORBextractor(*PARAMS, width=W, height=H, device=local_rank, max_batch=SUB)
+    cap = exL.capacity
+    tstream = torch.cuda.Stream()
+    torch.cuda.set_stream(tstream)
+    st = tstream.cuda_stream
+    d_match = torch.empty((SUB, cap), dtype=torch.int32, device="cuda") if fisheye else None
+    fb = W * H
+
+    def match(stream):
+        if fisheye:
+            M.fisheye_match_batch_device(exL, exR, SUB, 0.7, d_match.data_ptr(), None, stream)
+        else:
+            M.compute_stereo_matches(exL, exR, SUB, MBF, 0.0, FX, stream)
+
+    def step():
+        for s0 in range(0, P, SUB):
+            exL.extract_batch_device(dL.data_ptr() + s0 * fb, SUB, LAP, st)
+            exR.extract_batch_device(dR.data_ptr() + s0 * fb, SUB, LAP, st)
+            match(st)
+
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        step()
+    e1.record()
+    barrier()
+    ms_step = max_over_ranks(e0.elapsed_time(e1) / args.steps)
+    value = 2 * P * world / (ms_step / 1e3)
+    for ex in (exL, exR):
+        _lib.check(L.orbfe_set_profiling(ex.handle, 1))
+    for _ in range(args.steps):
+        step()
+    torch.cuda.synchronize()
+    stage_ms = np.zeros(8)
+    launches = C.c_int64(0)
+    for ex in (exL, exR):
+        buf = (C.c_double * 8)()
+        _lib.check(L.orbfe_stage_times(ex.handle, buf, C.byref(launches)))
+        stage_ms += np.array(list(buf))
+        _lib.check(L.orbfe_set_profiling(ex.handle, 0))
+    clocks = sampler.stop()
+    cnt, _ = exL.batch_counts(SUB)
+    cntR, _ = exR.batch_counts(SUB)
+    nkp = float(np.mean(np.concatenate([cnt, cntR])))
+    per_stage_bytes, total_bytes = algorithmic_bytes(nkp)
+    stage_ms_per_step = stage_ms / args.steps
+    top = int(np.argmax(stage_ms_per_step[:6]))
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except OSError:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    top_bytes = per_stage_bytes[STAGES[top]] * 2 * P
+    achieved = top_bytes / (stage_ms_per_step[top] / 1e3) / 1e9
+    roofline = {"bound": "hbm", "kernel": STAGES[top], "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured copy)" if peaks else "fallback 6650 GB/s",
+                "algorithmic_bytes_per_launch": top_bytes, "launch_ms": float(stage_ms_per_step[top]),
+                "stage_ms_per_step": {s: float(v) for s, v in zip(STAGES, stage_ms_per_step)},
+                "whole_step": {"algorithmic_bytes_per_frame": total_bytes, "achieved": total_bytes * 2 * P / (ms_step / 1e3) / 1e9,
+                               "frac": total_bytes * 2 * P / (ms_step / 1e3) / 1e9 / peak}}
+
+    # end to end from pinned host memory: every sub-batch uploads its images and downloads its results
+    def out_set():
+        side = lambda: (np.zeros(SUB, np.int32), np.zeros(SUB, np.int32),  # noqa: E731
+                        torch.empty((SUB, cap, 28), dtype=torch.uint8, pin_memory=True).numpy().view(_lib.KP_DTYPE).reshape(SUB, cap),
+                        torch.empty((SUB, cap, 32), dtype=torch.uint8, pin_memory=True).numpy())
+        return side() + side() + (torch.empty((SUB, cap), dtype=torch.float32, pin_memory=True).numpy(), torch.empty((SUB, cap), dtype=torch.float32, pin_memory=True).numpy())
+    hLn, hRn = hL.numpy(), hR.numpy()
+    subs = list(range(0, P, SUB))
+    if fisheye:
+        outs = [out_set()]
+        h_match = torch.empty((SUB, cap), dtype=torch.int32, pin_memory=True)
+        call = "orbfe_extract_batch_host x 2 + orbfe_fisheye_match_batch_device + download of the matches (synchronous)"
+
+        def e2e_run(nsteps):
+            for _ in range(nsteps):
+                for s0 in subs:
+                    exL.extract_batch_host(hLn[s0:s0 + SUB], LAP, outs[0][0:4])
+                    exR.extract_batch_host(hRn[s0:s0 + SUB], LAP, outs[0][4:8])
+                    M.fisheye_match_batch_device(exL, exR, SUB, 0.7, d_match.data_ptr(), None, st)
+                    h_match.copy_(d_match, non_blocking=True)
+                    torch.cuda.synchronize()
+        d2h = 2 * P * (cap * 60 + 8) + P * cap * 4
+    else:
+        outs = [out_set(), out_set()]
+        call = "orbfe_stereo_frames_submit / _wait, two sub-batches in flight"
+
+        def e2e_run(nsteps):
+            seq = [s0 for _ in range(nsteps) for s0 in subs]
+            M.stereo_frames_submit(exL, exR, hLn[seq[0]:seq[0] + SUB], hRn[seq[0]:seq[0] + SUB], MBF, 0.0, FX, LAP, outs[0])
+            for k in range(1, len(seq)):
+                M.stereo_frames_submit(exL, exR, hLn[seq[k]:seq[k] + SUB], hRn[seq[k]:seq[k] + SUB], MBF, 0.0, FX, LAP, outs[k & 1])
+                M.stereo_frames_wait(exL, exR, outs[(k - 1) & 1])
+            M.stereo_frames_wait(exL, exR, outs[(len(seq) - 1) & 1])
+        d2h = 2 * P * (cap * 60 + 8) + 2 * P * cap * 4
+    e2e_run(2)
+    barrier()
+    t0 = time.perf_counter()
+    e2e_run(args.steps)
+    torch.cuda.synchronize()
+    e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3 / args.steps)
+    barrier()
+    e2e = {"value": 2 * P * world / (e2e_ms / 1e3), "unit": "frames/s", "ms_per_step": e2e_ms, "call": call,
+           "fraction_of_device_resident": ms_step / e2e_ms, "h2d_gbs_reached_in_step": 2 * P * W * H / (e2e_ms / 1e3) / 1e9,
+           "h2d_bytes_per_step": 2 * P * W * H, "d2h_bytes_per_step": d2h}
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cores = os.cpu_count() or 1
+        sample = max(8 * cores, 32)
+        kind = "reference" if reference_available() else "port"
+        rate, dt = cpu_oracle_rate(sample, cores, kind)
+        cpu = dict({"value": rate, "unit": "frames/s", "cores": cores, "kind": kind,
+                    "sample": "%d stereo pairs (%.1f s wall) frame-parallel over %d threads; built -O3 -march=x86-64-v3" % (sample, dt, cores)},
+                   **cv2_lines(2 * cores, cores))
+    if rank == 0:
+        nsub = len(subs)
+        line = {"metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step,
+                "higher_is_better": True, "scaling": wl["scaling"], "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+                "config": {"workload": WORKLOAD, "pairs_per_gpu_per_step": P, "frames_per_step": 2 * P * world, "sub_batch_pairs": SUB,
+                           "distinct_pairs": min(P, 64), "lapping": list(LAP), "matching": wl["match"],
+                           "l2": "inputs_larger_than_L2 (%d MB of images per step per GPU)" % (2 * P * W * H >> 20),
+                           "mean_keypoints_per_frame": nkp, "parallelism": "frames sharded by rank, no collective"},
+                "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
+                "gpu_launches": nsub * (2 * (PARAMS[2] + 8) + (1 if fisheye else 3)) * args.steps}
+        print(json.dumps(line), flush=True)
 
 
 def main():
@@ -217,7 +504,9 @@ def main():
     ap.add_argument("--hamming-queries", type=int, default=4096)
     ap.add_argument("--hamming-db", type=int, default=1 << 20)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", default="euroc", choices=sorted(WORKLOADS), help="euroc = BASELINE.json's headline config (default); kitti, tumvi = configs 4 and 3")
     args = ap.parse_args()
+    wl = set_workload(args.workload)
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -251,6 +540,12 @@ def main():
         t = torch.tensor([x], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
+
+    if args.workload != "euroc":
+        run_workload(args, wl, rank, world, local_rank, barrier, max_over_ranks)
+        if world > 1:
+            dist.destroy_process_group()
+        return
 
     P = args.pairs
     hL, hR = gen_pairs(P, rank * 1000003, pin=True)
@@ -313,19 +608,31 @@ def main():
     peak = float(peaks.get("hbm_gbs", 6650.0))
     top_bytes = per_stage_bytes[STAGES[top]] * 2 * P
     achieved = top_bytes / (stage_ms_per_step[top] / 1e3) / 1e9 if stage_ms_per_step[top] > 0 else 0.0
-    traffic = None
-    try:   # DRAM bytes of the stage from the committed `ncu --set full` capture (profiles/r1_traffic.json), per launch
-        tj = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json")))
+    traffic, issue = None, None
+    try:   # DRAM bytes and executed warp instructions of the stage from the committed `ncu --set full` capture, per launch
+        tj = json.load(open(os.path.join(ROOT, "profiles", "r2_traffic.json")))
         traffic = tj["dram_bytes_per_frame"].get(STAGES[top])
         traffic = None if traffic is None else traffic * 2 * P
-    except (OSError, KeyError, ValueError):
+        # the issue roofline: every SM sub-partition issues at most one warp instruction per clock, so a stage that executes
+        # I warp instructions cannot finish before I / (148 SM x 4 x SM clock); all extraction kernels sit against this bound, not HBM
+        clk = float(clocks.get("sm_mhz") or peaks_for_issue()) * 1e6
+        issue_peak = 148 * 4 * clk
+        wi = tj["warp_instructions_per_frame"]
+        ext = sum(wi[k] for k in ("pyramid", "fast", "blur", "quadtree", "assemble", "orient_describe"))
+        issue = {"bound": "instruction issue (148 SM x 4 sub-partitions x SM clock)", "peak_warp_instructions_per_s": issue_peak,
+                 "stage_warp_instructions_per_frame": wi.get(STAGES[top]), "stage_frac": wi[STAGES[top]] * 2 * P / (stage_ms_per_step[top] / 1e3) / issue_peak,
+                 "whole_step_warp_instructions_per_frame": ext + wi["stereo"] / 2,
+                 "whole_step_frac": (ext * 2 * P + wi["stereo"] * P) / (ms_step / 1e3) / issue_peak,
+                 "frames_per_s_at_full_issue": issue_peak / (ext + wi["stereo"] / 2),
+                 "source": "smsp__inst_executed.sum per kernel, profiles/r2_traffic.json (ncu --set full of tools/prof_step.py, 64 pairs)"}
+    except (OSError, KeyError, ValueError, TypeError):
         pass
-    stage_kernels = {"pyramid": "k_pyramid_copy0 + 7 x k_pyramid_level + k_pyramid_borders",
-                     "fast": "k_fast_stream + k_fast_nms + k_fast_cells_list", "blur": "k_blur7 (all levels in one launch)", "quadtree": "k_quadtree",
+    stage_kernels = {"pyramid": "k_pyramid_copy0 + 7 x k_pyramid_level + k_pyramid_fringe",
+                     "fast": "k_fast_stream + k_fast_nms + k_fast_cells_list", "blur": "k_blur7_tma (all levels in one launch)", "quadtree": "k_quadtree",
                      "assemble": "k_assemble", "orient_describe": "k_orient_describe"}
     roofline = {"bound": "hbm", "kernel": STAGES[top], "kernels": stage_kernels.get(STAGES[top]), "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak, "traffic": traffic,
-                "limiter": "integer issue (ncu: ALU pipe ~70 % busy, DRAM ~6 % of peak; profiles/r1_kernels_full.txt), not HBM",
+                "frac": achieved / peak, "traffic": traffic, "issue": issue,
+                "limiter": "instruction issue (ncu: issue slots 72 % busy, ALU pipe 66 %, DRAM 6 % of peak; profiles/r2_kernels_full.txt), not HBM",
                 "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured copy)" if peaks else "fallback 6650 GB/s",
                 "algorithmic_bytes_per_launch": top_bytes,
                 "launch_ms": float(stage_ms_per_step[top]),
@@ -514,15 +821,21 @@ def main():
     barrier()
     ham_ms = max_over_ranks(e0.elapsed_time(e1) / args.steps)
     pairs_s = nq * ndb / (ham_ms / 1e3)
-    popc_peak = 148 * 16 * float(peaks.get("sm_max_mhz", 1965.0)) * 1e6 / 8.0   # pairs/s/GPU at 8 POPC per pair
+    popc_nominal = 148 * 16 * float(peaks.get("sm_max_mhz", 1965.0)) * 1e6       # POPC/s/GPU: 16 per clock per SM (nominal)
+    popc_measured = C.c_double(0.0)
+    _lib.check(L.orbfe_probe_popc(local_rank, C.byref(popc_measured)))            # POPC/s/GPU measured on this GPU just now (k_probe_popc)
+    popc_peak = popc_measured.value / 8.0                                         # pairs/s/GPU at 8 algorithmic POPC per pair
     hamming = {"value": pairs_s, "unit": "descriptor_pairs/s", "ms_per_step": ham_ms, "scaling": "strong",
                "queries": nq, "db_rows": ndb, "shards": world, "accepted": int(ham_out[0][:, 3].sum().item()),
                "call": "orbfe_hamming_top2_sharded (shard search + ncclAllGather + merge enqueued by one C call)",
                "torch_distributed_all_gather_path_ms": harness_ms,
                "roofline": {"bound": "int_popc", "achieved": pairs_s / world, "peak": popc_peak, "unit": "pairs/s/GPU",
                             "frac": pairs_s / world / popc_peak,
-                            "peak_source": "148 SM x 16 POPC/clk x sm_max_mhz / 8 POPC per pair (nominal; SURVEY.md §8d)",
-                            "note": "accounting stays at 8 algorithmic POPC per pair; the kernel issues 6 (two carry-save adders), so > 1.0 is possible"}}
+                            "peak_source": "measured in this run: orbfe_probe_popc (eight independent POPC chains per thread) / 8 POPC per pair",
+                            "popc_per_s_measured": popc_measured.value, "popc_per_s_nominal": popc_nominal,
+                            "frac_of_issued_popc_bound": pairs_s / world / (popc_measured.value / 6.0),
+                            "note": "accounting stays at 8 algorithmic POPC per pair; the kernel issues 6 (two carry-save adders), so frac > 1.0 is possible; "
+                                    "frac_of_issued_popc_bound divides by the POPC rate / 6, the bound of the instruction stream as written"}}
 
     # ---- projection-gated search: Tracking::SearchLocalPoints-sized frames, one CTA per frame
     from orb_slam3_detailed_comments_kor_b200 import projection as PJ
@@ -597,11 +910,17 @@ def main():
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cores = os.cpu_count() or 1
         sample = max(16 * cores, 64)
-        rate, dt = cpu_oracle_rate(sample, cores)
+        kind = "reference" if reference_available() else "port"
+        rate, dt = cpu_oracle_rate(sample, cores, kind)
+        port_rate, _ = cpu_oracle_rate(sample, cores, "port") if kind == "reference" else (rate, dt)
         hrate, hdt = cpu_hamming_rate(nq, ndb, cores)
-        cpu = {"value": rate, "unit": "frames/s", "cores": cores, "kind": "port",
-               "sample": "%d stereo pairs (%.1f s wall) frame-parallel over %d threads; oracle built -O3 -march=x86-64-v3" % (sample, dt, cores),
+        cpu = {"value": rate, "unit": "frames/s", "cores": cores, "kind": kind,
+               "sample": "%d stereo pairs (%.1f s wall) frame-parallel over %d threads; %s, built -O3 -march=x86-64-v3" % (
+                   sample, dt, cores, "the reference's own ORBextractor.cc + Frame::ComputeStereoMatches (oracle/_ref; OpenCV primitives = scalar "
+                   "restatements pinned to cv2 4.13)" if kind == "reference" else "CPU oracle restatement"),
+               "port_frames_per_s": port_rate,
                "hamming": {"value": hrate, "unit": "descriptor_pairs/s", "sample": "%d queries x %d rows (%.1f s wall)" % (nq, ndb, hdt)}}
+        cpu.update(cv2_lines(2 * cores, cores))
         from oracle import orb_oracle as O
         reps = 64 * cores
 

@@ -266,8 +266,18 @@ inline void FAST(InputArray _image, std::vector<KeyPoint>& keypoints, int thresh
     assert(nonmaxSuppression);
     (void)nonmaxSuppression;
     Mat im = _image.getMat();
-    std::vector<orc_keypoint> out((size_t)im.rows * im.cols + 1);
-    int n = orc_fast9_16(im.data, im.cols, im.rows, (int)im.step, threshold, out.data(), (int)out.size());
+    /* scratch for the detector's output: one malloc'd block per thread, grown on demand and reused by every cell (plain malloc, so it
+     * is neither zero-filled per call nor part of ref_shim.cpp's per-call arena) */
+    static thread_local orc_keypoint* out = nullptr;
+    static thread_local size_t outCap = 0;
+    const size_t need = (size_t)im.rows * im.cols + 1;
+    if (need > outCap) {
+        std::free(out);
+        out = (orc_keypoint*)std::malloc(need * sizeof(orc_keypoint));
+        outCap = out ? need : 0;
+        if (!out) std::abort();
+    }
+    int n = orc_fast9_16(im.data, im.cols, im.rows, (int)im.step, threshold, out, (int)outCap);
     keypoints.clear();
     keypoints.reserve(n);
     for (int i = 0; i < n; ++i) keypoints.push_back(KeyPoint(out[i].x, out[i].y, out[i].size, out[i].angle, out[i].response, out[i].octave, out[i].class_id));

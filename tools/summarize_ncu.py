@@ -76,11 +76,14 @@ def table(src, dst, frames):
             ("issue%", "smsp__issue_active.avg.pct_of_peak_sustained_active"), ("alu%", "sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active"),
             ("xu%", "sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active"), ("lsu%", "sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active"),
             ("dram%", "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed"), ("warps%", "sm__warps_active.avg.pct_of_peak_sustained_active"),
+            ("fma%", "sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active"),
             ("regs", "launch__registers_per_thread"), ("winst", "smsp__inst_executed.sum")]
     stage_of = {"k_pyramid_copy0": "pyramid", "k_pyramid_level": "pyramid", "k_pyramid_borders": "pyramid", "k_pyramid_fringe": "pyramid", "k_fast_stream": "fast",
-                "k_fast_nms": "fast", "k_fast_cells_list": "fast", "k_blur7": "blur", "k_quadtree": "quadtree", "k_assemble": "assemble",
+                "k_fast_nms": "fast", "k_fast_cells_list": "fast", "k_blur7": "blur", "k_blur7_tma": "blur", "k_quadtree": "quadtree",
+                "void k_quadtree<0>": "quadtree", "void k_quadtree<1>": "quadtree", "k_assemble": "assemble",
                 "k_orient_describe": "orient_describe", "k_stereo_bucket": "stereo", "k_stereo_match": "stereo", "k_stereo_median": "stereo"}
-    seen, traffic, times = {}, collections.OrderedDict(), collections.OrderedDict()
+    seen, traffic, times, winst = {}, collections.OrderedDict(), collections.OrderedDict(), collections.OrderedDict()
+    per_kernel = collections.OrderedDict()
     with open(dst, "w") as f:
         f.write("# ncu --set full --clock-control none, one whole step of bench.py (%d frames per launch); source: %s\n" % (frames, src))
         f.write("%-20s %-15s " % ("kernel", "grid") + " ".join("%10s" % n for n, _ in cols) + "  top stalls (per issue)\n")
@@ -98,7 +101,18 @@ def table(src, dst, frames):
                 mb = float(r[c("dram__bytes_read.sum")]) + float(r[c("dram__bytes_write.sum")])
                 traffic[stg] = traffic.get(stg, 0.0) + mb * 1e6 / frames
                 times[stg] = times.get(stg, 0.0) + float(r[c("gpu__time_duration.sum")])
-    json.dump({"frames_per_launch": frames, "dram_bytes_per_frame": traffic, "stage_us_under_ncu": times, "source": src},
+                wi = float(r[c("smsp__inst_executed.sum")])
+                winst[stg] = winst.get(stg, 0.0) + wi / frames
+                k = per_kernel.setdefault(name, {"warp_instructions_per_frame": 0.0, "us_under_ncu": 0.0, "launches": 0})
+                k["warp_instructions_per_frame"] += wi / frames
+                k["us_under_ncu"] += float(r[c("gpu__time_duration.sum")])
+                k["launches"] += 1
+                for label, metric in (("issue_pct", "smsp__issue_active.avg.pct_of_peak_sustained_active"), ("alu_pct", "sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active"),
+                                      ("fma_pct", "sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active"), ("lsu_pct", "sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active"),
+                                      ("xu_pct", "sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active")):
+                    k[label] = max(k.get(label, 0.0), float(r[c(metric)]))   # of the largest launch of that kernel
+    json.dump({"frames_per_launch": frames, "dram_bytes_per_frame": traffic, "stage_us_under_ncu": times,
+               "warp_instructions_per_frame": winst, "per_kernel": per_kernel, "source": src},
               open(dst.replace("_kernels_full.txt", "_traffic.json"), "w"), indent=1)
     print(open(dst).read())
 
