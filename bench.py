@@ -41,7 +41,7 @@ WORKLOADS = {
                   name="kitti_stereo_1241x376_2000feat_4096_images_extract+ComputeStereoMatches", metric="orb_frames_per_sec_1241x376_2000feat"),
     # Examples/Stereo-Inertial/TUM_512.yaml:42-46 (lapping 0..511 on both cameras), knn-2 + 0.7 of ComputeStereoFishEyeMatches
     "tumvi": dict(W=512, H=512, params=(1500, 1.2, 8, 20, 7), mbf=0.0, fx=0.0, lap=(0, 511), match="fisheye", scaling="weak",
-                  name="tumvi_fisheye_stereo_2x512x512_1500feat_lapping_extract+knn2_ratio", metric="orb_frames_per_sec_512x512_1500feat"),
+                  name="tumvi_fisheye_stereo_2x512x512_1500feat_lapping_extract+ComputeStereoFishEyeMatches", metric="orb_frames_per_sec_512x512_1500feat"),
 }
 
 
@@ -367,10 +367,21 @@ def run_workload(args, wl, rank, world, local_rank, barrier, max_over_ranks):
     st = tstream.cuda_stream
     d_match = torch.empty((SUB, cap), dtype=torch.int32, device="cuda") if fisheye else None
     fb = W * H
+    if fisheye:   # Examples/Stereo-Inertial/TUM_512.yaml:9-35: the two KannalaBrandt8 cameras and Tlr
+        cam1 = [190.97847715128717, 190.9733070521226, 254.93170605935475, 256.8974428996504,
+                0.0034823894022493434, 0.0007150348452162257, -0.0020532361418706202, 0.00020293673591811182]
+        cam2 = [190.44236969414825, 190.4344384721956, 252.59949716835982, 254.91723064636983,
+                0.0034003170790442797, 0.001766278153469831, -0.00266312569781606, 0.0003299517423931039]
+        Rlr = [0.999999445773493, 0.000791687752817, 0.000694034010224, -0.000823363992158, 0.998899461915674, 0.046895490788700,
+               -0.000656143613644, -0.046896036240590, 0.998899560146304]
+        tlr = [0.101063427414194, 0.001946204678584, 0.001015350132563]
+        d_rl = torch.empty((SUB, cap), dtype=torch.int32, device="cuda")
+        d_depth, d_p3d = torch.empty((SUB, cap), device="cuda"), torch.empty((SUB, cap, 3), device="cuda")
 
     def match(stream):
-        if fisheye:
+        if fisheye:   # Frame::ComputeStereoFishEyeMatches: knn-2 + 0.7 ratio, then TriangulateMatches and the depth test
             M.fisheye_match_batch_device(exL, exR, SUB, 0.7, d_match.data_ptr(), None, stream)
+            M.fisheye_triangulate_batch_device(exL, exR, SUB, cam1, cam2, Rlr, tlr, d_match.data_ptr(), d_rl.data_ptr(), d_depth.data_ptr(), d_p3d.data_ptr(), stream)
         else:
             M.compute_stereo_matches(exL, exR, SUB, MBF, 0.0, FX, stream)
 
@@ -439,17 +450,19 @@ def run_workload(args, wl, rank, world, local_rank, barrier, max_over_ranks):
     if fisheye:
         outs = [out_set()]
         h_match = torch.empty((SUB, cap), dtype=torch.int32, pin_memory=True)
-        call = "orbfe_extract_batch_host x 2 + orbfe_fisheye_match_batch_device + download of the matches (synchronous)"
+        h_depth = torch.empty((SUB, cap), dtype=torch.float32, pin_memory=True)
+        call = "orbfe_extract_batch_host x 2 + orbfe_fisheye_match_batch_device + orbfe_fisheye_triangulate_batch_device + download of matches and depths (synchronous)"
 
         def e2e_run(nsteps):
             for _ in range(nsteps):
                 for s0 in subs:
                     exL.extract_batch_host(hLn[s0:s0 + SUB], LAP, outs[0][0:4])
                     exR.extract_batch_host(hRn[s0:s0 + SUB], LAP, outs[0][4:8])
-                    M.fisheye_match_batch_device(exL, exR, SUB, 0.7, d_match.data_ptr(), None, st)
+                    match(st)
                     h_match.copy_(d_match, non_blocking=True)
+                    h_depth.copy_(d_depth, non_blocking=True)
                     torch.cuda.synchronize()
-        d2h = 2 * P * (cap * 60 + 8) + P * cap * 4
+        d2h = 2 * P * (cap * 60 + 8) + 2 * P * cap * 4
     else:
         outs = [out_set(), out_set()]
         call = "orbfe_stereo_frames_submit / _wait, two sub-batches in flight"
@@ -490,7 +503,7 @@ def run_workload(args, wl, rank, world, local_rank, barrier, max_over_ranks):
                            "l2": "inputs_larger_than_L2 (%d MB of images per step per GPU)" % (2 * P * W * H >> 20),
                            "mean_keypoints_per_frame": nkp, "parallelism": "frames sharded by rank, no collective"},
                 "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
-                "gpu_launches": nsub * (2 * (PARAMS[2] + 8) + (1 if fisheye else 3)) * args.steps}
+                "gpu_launches": nsub * (2 * (PARAMS[2] + 8) + (2 if fisheye else 3)) * args.steps}
         print(json.dumps(line), flush=True)
 
 

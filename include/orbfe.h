@@ -241,6 +241,28 @@ int orbfe_knn2_ratio(int device, const uint8_t* q, int nq, const uint8_t* t, int
 int orbfe_fisheye_match_batch_device(orbfe_extractor* exL, orbfe_extractor* exR, int nframes, double ratio, int32_t* d_match_lr, int32_t* d_dist01,
                                      void* stream);
 
+/* The rest of Frame::ComputeStereoFishEyeMatches (src/Frame.cc:1145-1157) on the device: KannalaBrandt8::TriangulateMatches
+ * (src/CameraModels/KannalaBrandt8.cpp:338-407: unproject both keypoints, parallax test, Triangulate's 4x4 SVD, depth signs, the
+ * two reprojection tests at 5.991 * mvLevelSigma2[octave]) for every match that orbfe_fisheye_match_batch_device left in d_match_lr,
+ * and the `depth > 0.0001f` acceptance: rejected matches are reset to -1 in d_match_lr, accepted ones fill
+ *   d_match_rl [nframes*cap]   mvRightToLeftMatch (the last left keypoint that matched a right one keeps it, as the reference's loop),
+ *   d_depth    [nframes*cap]   mvDepth (-1 = none),
+ *   d_p3d      [nframes*cap*3] mvStereo3Dpoints (camera-1 coordinates; zeros where there is none).
+ * rig: mvParameters of mpCamera and mpCamera2 (fx, fy, cx, cy, k1..k4), mRlr row-major and mtlr (Frame.h, from Tlr of the settings).
+ * Arithmetic: OpenCV's as pinned by oracle/triangulate_oracle.cpp (4x4 SVD = cv2.SVDecomp bit for bit on the host); the device's
+ * tanf / atan2f / cosf / sinf differ from the host libm by an ulp or two, so depths agree to 1e-4 relative, not to the bit. */
+typedef struct {
+    float cam1[8], cam2[8];
+    float R12[9], t12[3];
+} orbfe_fisheye_rig;
+int orbfe_fisheye_triangulate_batch_device(orbfe_extractor* exL, orbfe_extractor* exR, int nframes, const orbfe_fisheye_rig* rig, int32_t* d_match_lr,
+                                           int32_t* d_match_rl, float* d_depth, float* d_p3d, void* stream);
+/* KannalaBrandt8::TriangulateMatches (src/CameraModels/KannalaBrandt8.cpp:338-407) for n keypoint pairs given as plain device arrays:
+ * d_uv1 / d_uv2 [n][2] pixel coordinates in camera 1 / 2, d_sigma1 / d_sigma2 [n] = mvLevelSigma2 of their octaves;
+ * d_depth[i] = the function's return value (-1 when it rejects the pair), d_p3d [n][3] = p3D.  Asynchronous on `stream`. */
+int orbfe_kb8_triangulate_pairs_device(int device, const orbfe_fisheye_rig* rig, const float* d_uv1, const float* d_uv2, const float* d_sigma1,
+                                       const float* d_sigma2, int n, float* d_depth, float* d_p3d, void* stream);
+
 /* ------------------------------------------------------------------------------------ bag-of-words assignment (N2) */
 /* Replaces Frame::ComputeBoW / KeyFrame::ComputeBoW (src/Frame.cc:724-731, src/KeyFrame.cc:105-114):
  *   mpORBvocabulary->transform(vCurrentDesc, mBowVec, mFeatVec, 4)

@@ -19,7 +19,8 @@ MATCH_DTYPE = np.dtype([("best1", "<i4"), ("best2", "<i4"), ("idx", "<i4"), ("ac
 
 def build(force=False):
     """Compile the oracle with its Makefile (gcc only; no reference sources are read)."""
-    srcs = [os.path.join(_HERE, f) for f in ("orb_oracle.cpp", "match_oracle.cpp", "condition_oracle.cpp", "orb_oracle.h", "Makefile")]
+    srcs = [os.path.join(_HERE, f) for f in ("orb_oracle.cpp", "match_oracle.cpp", "condition_oracle.cpp", "project_oracle.cpp", "bow_oracle.cpp",
+                                             "triangulate_oracle.cpp", "orb_oracle.h", "Makefile")]
     if force or not os.path.exists(_SO) or any(os.path.getmtime(s) > os.path.getmtime(_SO) for s in srcs):
         subprocess.check_call(["make", "-C", _HERE, "liborb_oracle.so"], stdout=subprocess.DEVNULL)
     return _SO
@@ -77,6 +78,10 @@ def lib():
     L.orc_search_by_projection.restype = C.c_int
     L.orc_clahe_u8.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_double, C.c_int, C.c_int, vp, C.c_int, vp]
     L.orc_clahe_u8.restype = C.c_int
+    L.orc_svd4x4_vt.argtypes = [vp, vp, vp]
+    L.orc_kb8_unproject.argtypes = [vp, C.c_float, C.c_float, vp]
+    L.orc_kb8_project.argtypes = [vp, vp, vp]
+    L.orc_kb8_triangulate_matches.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, C.c_int, vp, vp]
     _lib = L
     return L
 
@@ -374,3 +379,35 @@ def merge_top2_host(parts, th, ratio, strict_lt):
     th_ok = (b1 < th) if strict_lt else (b1 <= th)
     out["accepted"] = th_ok & (b1.astype(np.float32) < np.float32(ratio) * b2.astype(np.float32))
     return out
+
+
+def svd4x4_vt(A):
+    """cv::SVD::compute(A, w, u, vt, MODIFY_A | FULL_UV) for a 4x4 float32 matrix: (w[4], vt[4, 4])."""
+    A = np.ascontiguousarray(A, np.float32)
+    w, vt = np.zeros(4, np.float32), np.zeros((4, 4), np.float32)
+    lib().orc_svd4x4_vt(_ptr(A), _ptr(w), _ptr(vt))
+    return w, vt
+
+
+def kb8_unproject(params, u, v):
+    p = np.ascontiguousarray(params, np.float32)
+    out = np.zeros(3, np.float32)
+    lib().orc_kb8_unproject(_ptr(p), float(u), float(v), _ptr(out))
+    return out
+
+
+def kb8_project(params, p3):
+    p, x = np.ascontiguousarray(params, np.float32), np.ascontiguousarray(p3, np.float32)
+    out = np.zeros(2, np.float32)
+    lib().orc_kb8_project(_ptr(p), _ptr(x), _ptr(out))
+    return out
+
+
+def kb8_triangulate_matches(cam1, cam2, R12, t12, uv1, uv2, sigma1, sigma2):
+    """KannalaBrandt8::TriangulateMatches per keypoint pair: (depth[n] (-1 = rejected), p3d[n, 3])."""
+    c = lambda a: np.ascontiguousarray(a, np.float32)  # noqa: E731
+    cam1, cam2, R12, t12, uv1, uv2, sigma1, sigma2 = c(cam1), c(cam2), c(R12), c(t12), c(uv1), c(uv2), c(sigma1), c(sigma2)
+    n = uv1.shape[0]
+    depth, p3d = np.zeros(n, np.float32), np.zeros((n, 3), np.float32)
+    lib().orc_kb8_triangulate_matches(_ptr(cam1), _ptr(cam2), _ptr(R12), _ptr(t12), _ptr(uv1), _ptr(uv2), _ptr(sigma1), _ptr(sigma2), n, _ptr(depth), _ptr(p3d))
+    return depth, p3d

@@ -58,6 +58,8 @@ SIGNATURES = {
     "orbfe_pyramid_levels": (i32, [vp, i32, i32, vp]),
     "orbfe_probe_popc": (i32, [i32, C.POINTER(C.c_double)]),
     "orbfe_fisheye_match_batch_device": (i32, [vp, vp, i32, C.c_double, vp, vp, vp]),
+    "orbfe_fisheye_triangulate_batch_device": (i32, [vp, vp, i32, vp, vp, vp, vp, vp, vp]),
+    "orbfe_kb8_triangulate_pairs_device": (i32, [i32, vp, vp, vp, vp, vp, i32, vp, vp, vp]),
     "orbfe_pin_host": (i32, [vp, sz]),
     "orbfe_unpin_host": (i32, [vp]),
     "orbfe_blurred_level": (i32, [vp, i32, i32, vp]),

@@ -136,6 +136,25 @@ def fisheye_match_batch_device(exL, exR, nframes, ratio, d_match_lr, d_dist01=No
                                                       C.c_void_p(d_dist01) if d_dist01 else None, C.c_void_p(stream) if stream else None))
 
 
+def fisheye_triangulate_batch_device(exL, exR, nframes, cam1, cam2, R12, t12, d_match_lr, d_match_rl, d_depth, d_p3d, stream=None):
+    """KannalaBrandt8::TriangulateMatches + the depth test of Frame::ComputeStereoFishEyeMatches (src/Frame.cc:1145-1157) on the
+    matches fisheye_match_batch_device produced; cam1 / cam2 = mvParameters (8 floats), R12 / t12 = mRlr, mtlr."""
+    rig = np.concatenate([np.asarray(cam1, np.float32).reshape(8), np.asarray(cam2, np.float32).reshape(8), np.asarray(R12, np.float32).reshape(9),
+                          np.asarray(t12, np.float32).reshape(3)]).astype(np.float32)
+    check(_lib.lib().orbfe_fisheye_triangulate_batch_device(exL.handle, exR.handle, nframes, ptr(rig), C.c_void_p(d_match_lr), C.c_void_p(d_match_rl),
+                                                            C.c_void_p(d_depth), C.c_void_p(d_p3d), C.c_void_p(stream) if stream else None))
+
+
+def make_fisheye_rig(cam1, cam2, R12, t12):
+    return np.concatenate([np.asarray(cam1, np.float32).reshape(8), np.asarray(cam2, np.float32).reshape(8), np.asarray(R12, np.float32).reshape(9),
+                           np.asarray(t12, np.float32).reshape(3)]).astype(np.float32)
+
+
+def kb8_triangulate_pairs_device(rig, d_uv1, d_uv2, d_sigma1, d_sigma2, n, d_depth, d_p3d, device=0, stream=None):
+    check(_lib.lib().orbfe_kb8_triangulate_pairs_device(device, ptr(rig), C.c_void_p(d_uv1), C.c_void_p(d_uv2), C.c_void_p(d_sigma1), C.c_void_p(d_sigma2), n,
+                                                        C.c_void_p(d_depth), C.c_void_p(d_p3d), C.c_void_p(stream) if stream else None))
+
+
 def stereo_result(exL, frame):
     u = np.zeros(exL.capacity, np.float32)
     d = np.zeros(exL.capacity, np.float32)
