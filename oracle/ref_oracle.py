@@ -24,7 +24,8 @@ def so_path(fma=False):
 def build():
     """Run the committed recipe (oracle/Makefile) when the reference sources are present; otherwise keep what is there."""
     if os.path.exists(os.path.join(REF_SRC, "src", "ORBextractor.cc")):
-        subprocess.check_call(["make", "-C", _HERE, "REF=" + REF_SRC, "_ref/liborb_ref.so", "_ref/liborb_ref_fma.so"], stdout=subprocess.DEVNULL)
+        subprocess.check_call(["make", "-C", _HERE, "REF=" + REF_SRC, "_ref/liborb_ref.so", "_ref/liborb_ref_fma.so", "_ref/libdbow_ref.so"],
+                              stdout=subprocess.DEVNULL)
     return so_path() if os.path.exists(so_path()) else None
 
 
@@ -131,3 +132,71 @@ def set_arena(on, fma=False):
 
 def arena_peak(fma=False):
     return lib(fma).ref_arena_peak()
+
+
+# ---- the reference's vendored DBoW2 (Thirdparty/DBoW2), oracle/ref_dbow_shim.cpp -------------------------------------------------
+_dbow = None
+
+
+def dbow_path():
+    return os.path.join(_HERE, "_ref", "libdbow_ref.so")
+
+
+def dbow_available():
+    return os.path.exists(dbow_path()) or (build() is not None and os.path.exists(dbow_path()))
+
+
+def dbow_lib():
+    global _dbow
+    if _dbow is None:
+        if not dbow_available():
+            raise RuntimeError("oracle/_ref/libdbow_ref.so is not built and %s is absent" % REF_SRC)
+        L = C.CDLL(dbow_path())
+        vp = C.c_void_p
+        L.ref_voc_load_text.restype = vp
+        L.ref_voc_load_text.argtypes = [C.c_char_p]
+        L.ref_voc_destroy.argtypes = [vp]
+        L.ref_voc_words.argtypes = [vp]
+        L.ref_voc_transform.argtypes = [vp, vp, C.c_int, C.c_int, vp, vp, vp, vp, vp, vp, vp]
+        L.ref_voc_score.restype = C.c_double
+        L.ref_voc_score.argtypes = [vp, vp, vp, C.c_int, vp, vp, C.c_int]
+        _dbow = L
+    return _dbow
+
+
+def write_vocabulary_text(path, k, L, scoring, weighting, parent, is_leaf, desc, weight):
+    """The file ORBVocabulary::loadFromTextFile reads (TemplatedVocabulary.h:1338-1426): `k L scoring weighting`, then one line per
+    node `parent isLeaf d0 .. d31 weight`; no newline after the last node (the reader would turn an empty last line into a node)."""
+    lines = ["%d %d %d %d" % (k, L, scoring, weighting)]
+    for p, leaf, d, w in zip(parent, is_leaf, desc, weight):
+        lines.append("%d %d %s %s" % (int(p), int(leaf), " ".join(str(int(b)) for b in d), repr(float(w))))
+    with open(path, "w") as f:
+        f.write("\n".join(lines))
+
+
+class ReferenceVocabulary:
+    """ORB_SLAM3::ORBVocabulary (DBoW2::TemplatedVocabulary<FORB::TDescriptor, FORB>) itself, loaded from a text file."""
+
+    def __init__(self, path):
+        self.L = dbow_lib()
+        self.h = self.L.ref_voc_load_text(path.encode())
+        if not self.h:
+            raise ValueError("loadFromTextFile failed")
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.L.ref_voc_destroy(self.h)
+            self.h = None
+
+    def words(self):
+        return self.L.ref_voc_words(self.h)
+
+    def transform(self, desc, levelsup=4):
+        desc = np.ascontiguousarray(desc, np.uint8)
+        n = desc.shape[0]
+        bw, bv = np.zeros(max(n, 1), np.int32), np.zeros(max(n, 1), np.float64)
+        fn, fs, ff = np.zeros(max(n, 1), np.int32), np.zeros(n + 1, np.int32), np.zeros(max(n, 1), np.int32)
+        nb, nf = C.c_int32(0), C.c_int32(0)
+        self.L.ref_voc_transform(self.h, _ptr(desc), n, levelsup, _ptr(bw), _ptr(bv), C.byref(nb), _ptr(fn), _ptr(fs), _ptr(ff), C.byref(nf))
+        nb, nf = nb.value, nf.value
+        return {"bow_words": bw[:nb].copy(), "bow_values": bv[:nb].copy(), "feat_vec": {int(fn[e]): ff[fs[e]:fs[e + 1]].copy() for e in range(nf)}}

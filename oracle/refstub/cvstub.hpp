@@ -22,7 +22,10 @@
 #include <cstdlib>
 #include <cstring>
 #include <iterator>
+#include <iostream>
 #include <memory>
+#include <sstream>
+#include <string>
 #include <vector>
 
 #include "../orb_oracle.h"
@@ -32,6 +35,7 @@ typedef unsigned char uchar;
 #define CV_PI 3.1415926535897932384626433832795
 #define CV_8U 0
 #define CV_8UC1 0
+#define CV_32F 5   /* only FORB::toMat32F (Thirdparty/DBoW2/DBoW2/FORB.cpp:138-170, unused here) asks for it */
 
 /* cvRound = round half to even in the current (default) rounding mode, like OpenCV's SSE2 / lrint paths. */
 static inline int cvRound(double v) { return (int)std::lrint(v); }
@@ -97,12 +101,12 @@ public:
     uchar* data;
     Step step;
 
-    Mat() : rows(0), cols(0), data(nullptr), step{0}, origin(nullptr), wholeRows(0), wholeCols(0) {}
+    Mat() : rows(0), cols(0), data(nullptr), step{0}, origin(nullptr), wholeRows(0), wholeCols(0), type_(CV_8UC1) {}
     Mat(Size sz, int type) { alloc(sz.height, sz.width, type); }
     Mat(int r, int c, int type) { alloc(r, c, type); }
     /* header over caller memory (used by the C entry points of ref_shim.cpp, not by the reference) */
     Mat(int r, int c, int type, void* ext, size_t extStep)
-        : rows(r), cols(c), data((uchar*)ext), step{extStep}, origin((uchar*)ext), wholeRows(r), wholeCols(c) { assert(type == CV_8UC1); }
+        : rows(r), cols(c), data((uchar*)ext), step{extStep}, origin((uchar*)ext), wholeRows(r), wholeCols(c), type_(type) { assert(type == CV_8UC1); }
 
     static Mat zeros(int r, int c, int type) {
         Mat m(r, c, type);
@@ -110,7 +114,7 @@ public:
         return m;
     }
 
-    int type() const { return CV_8UC1; }
+    int type() const { return type_; }
     bool empty() const { return data == nullptr || rows == 0 || cols == 0; }
     size_t step1() const { return step.v; }
 
@@ -134,7 +138,7 @@ public:
     template <typename T> const T* ptr(int y = 0) const { return (const T*)(data + (size_t)y * step.v); }
 
     void create(int r, int c, int type) {
-        if (data && r == rows && c == cols) return;
+        if (data && r == rows && c == cols && type == type_) return;
         alloc(r, c, type);
     }
     void release() { *this = Mat(); }
@@ -160,12 +164,14 @@ private:
     std::shared_ptr<uchar> hold;
     uchar* origin;
     int wholeRows, wholeCols;
+    int type_;
 
     void alloc(int r, int c, int type) {
-        assert(type == CV_8UC1);
-        (void)type;
-        rows = r; cols = c; step.v = (size_t)c; wholeRows = r; wholeCols = c;
-        size_t n = (size_t)r * c;
+        assert(type == CV_8UC1 || type == CV_32F);
+        const size_t esz = type == CV_32F ? 4 : 1;   /* every view / pixel routine of this header is for the 8-bit case */
+        type_ = type;
+        rows = r; cols = c; step.v = (size_t)c * esz; wholeRows = r; wholeCols = c;
+        size_t n = (size_t)r * c * esz;
         hold = std::shared_ptr<uchar>(n ? new uchar[n] : nullptr, std::default_delete<uchar[]>());
         data = origin = hold.get();
     }
@@ -308,6 +314,31 @@ inline double norm(InputArray _a, InputArray _b, int normType) {
 struct KeyPointsFilter {
     static void retainBest(std::vector<KeyPoint>&, int) { std::abort(); }
 };
+
+/* cv::FileStorage / cv::FileNode: Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h names them in its YAML save / load members
+ * (:1452-1660).  The vocabulary under test is read with loadFromTextFile (:1338-1426), which uses no OpenCV; these only have to
+ * compile, and abort if anything ever calls them. */
+class FileNode {
+public:
+    FileNode operator[](const char*) const { std::abort(); }
+    FileNode operator[](const std::string&) const { std::abort(); }
+    FileNode operator[](int) const { std::abort(); }
+    size_t size() const { std::abort(); }
+    operator int() const { std::abort(); }
+    operator float() const { std::abort(); }
+    operator double() const { std::abort(); }
+    operator std::string() const { std::abort(); }
+};
+class FileStorage {
+public:
+    enum { READ = 0, WRITE = 1 };
+    FileStorage(const std::string&, int) {}
+    bool isOpened() const { return false; }
+    FileNode operator[](const std::string&) const { std::abort(); }
+    FileNode operator[](const char*) const { std::abort(); }
+    void release() {}
+};
+template <typename T> inline FileStorage& operator<<(FileStorage& fs, const T&) { std::abort(); return fs; }
 
 }  // namespace cv
 
