@@ -48,6 +48,7 @@ def lib(fma=False):
     L.ref_level_keypoints.argtypes = par + [vp, C.c_int, C.c_int, C.c_int, vp, C.c_int, vp]
     L.ref_stereo.argtypes = par + [vp, vp, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, vp, vp, i32p, vp, vp, i32p, C.c_int, vp, vp]
     L.ref_descriptor_distance.argtypes = [vp, vp]
+    L.ref_search_by_bow.argtypes = [vp, vp, C.c_int, vp, vp, vp, C.c_int, vp, vp, vp, C.c_int, vp, vp, vp, C.c_int, vp, C.c_int, C.c_float, C.c_int, C.c_int, vp]
     _libs[fma] = L
     return L
 
@@ -123,6 +124,24 @@ class ReferenceExtractor:
 def descriptor_distance(a, b, fma=False):
     a, b = np.ascontiguousarray(a, np.uint8), np.ascontiguousarray(b, np.uint8)
     return lib(fma).ref_descriptor_distance(_ptr(a), _ptr(b))
+
+
+def search_by_bow(desc_kf, kps_kf, fv_kf, has_map_point, desc_f, kps_f, fv_f, nnratio=0.7, check_orientation=True, kf_kf=False, has_map_point_f=None,
+                  n_left_f=-1):
+    """The reference's own ORBmatcher::SearchByBoW (KeyFrame*, Frame&) — or, with kf_kf, (KeyFrame*, KeyFrame*) — on arrays; same arguments as
+    orb_oracle.search_by_bow (has_map_point entries: 0 none, 1 good, 2 bad).  Returns (match, nmatches)."""
+    from .orb_oracle import _fv_arrays
+    desc_kf, desc_f = np.ascontiguousarray(desc_kf, np.uint8), np.ascontiguousarray(desc_f, np.uint8)
+    kps_kf, kps_f = np.ascontiguousarray(kps_kf, KP_DTYPE), np.ascontiguousarray(kps_f, KP_DTYPE)
+    na, sa, fa = _fv_arrays(fv_kf)
+    nb, sb, fb = _fv_arrays(fv_f)
+    mp = np.ascontiguousarray(has_map_point, np.uint8)
+    mpf = None if has_map_point_f is None else np.ascontiguousarray(has_map_point_f, np.uint8)
+    out = np.zeros(max(desc_kf.shape[0] if kf_kf else desc_f.shape[0], 1), np.int32)
+    nm = lib().ref_search_by_bow(_ptr(desc_kf), _ptr(kps_kf), desc_kf.shape[0], _ptr(na), _ptr(sa), _ptr(fa), len(na), _ptr(mp), _ptr(desc_f), _ptr(kps_f),
+                                 desc_f.shape[0], _ptr(nb), _ptr(sb), _ptr(fb), len(nb), _ptr(mpf) if mpf is not None else None, int(n_left_f), nnratio,
+                                 int(check_orientation), int(kf_kf), _ptr(out))
+    return out[:(desc_kf.shape[0] if kf_kf else desc_f.shape[0])], nm
 
 
 def set_arena(on, fma=False):

@@ -21,7 +21,8 @@
 #include <new>
 
 #include "refstub/cvstub.hpp"
-#include "ORBextractor.h" /* the reference's header: -I/root/reference/include */
+#include "FeatureVector.h" /* the reference's vendored DBoW2 (Thirdparty/DBoW2/DBoW2): the real FeatureVector type */
+#include "ORBextractor.h"  /* the reference's header: -I/root/reference/include */
 
 /* ---- bump arena ------------------------------------------------------------------------------------------------ */
 namespace {
@@ -97,28 +98,59 @@ void operator delete[](void* p, size_t) noexcept { arena_delete(p); }
 using namespace std;
 namespace ORB_SLAM3 {
 
-class ORBmatcher {
+/* only what the cut-out bodies name: include/MapPoint.h (isBad), include/KeyFrame.h and include/Frame.h (the members below) */
+class MapPoint {
 public:
-    static int DescriptorDistance(const cv::Mat& a, const cv::Mat& b);
-    static const int TH_LOW;
-    static const int TH_HIGH;
+    bool bad = false;
+    bool isBad() { return bad; }
 };
 
 class Frame {
 public:
     void ComputeStereoMatches();
     int N;
+    int Nleft = -1;
     float mbf, mb;
     ORBextractor *mpORBextractorLeft, *mpORBextractorRight;
-    std::vector<cv::KeyPoint> mvKeys, mvKeysRight;
+    std::vector<cv::KeyPoint> mvKeys, mvKeysRight, mvKeysUn;
     cv::Mat mDescriptors, mDescriptorsRight;
     std::vector<float> mvuRight, mvDepth;
     std::vector<float> mvScaleFactors, mvInvScaleFactors;
+    DBoW2::FeatureVector mFeatVec;
+    void* mpCamera2 = nullptr;   /* GeometricCamera*: only tested against NULL by the bodies taken here */
 };
+
+class KeyFrame {
+public:
+    std::vector<MapPoint*> GetMapPointMatches() { return mvpMapPoints; }
+    std::vector<MapPoint*> mvpMapPoints;
+    DBoW2::FeatureVector mFeatVec;
+    cv::Mat mDescriptors;
+    int NLeft = -1;
+    std::vector<cv::KeyPoint> mvKeys, mvKeysRight, mvKeysUn;
+    void* mpCamera2 = nullptr;
+};
+
+class ORBmatcher {
+public:
+    ORBmatcher(float nnratio = 0.6, bool checkOri = true) : mfNNratio(nnratio), mbCheckOrientation(checkOri) {}
+    static int DescriptorDistance(const cv::Mat& a, const cv::Mat& b);
+    int SearchByBoW(KeyFrame* pKF, Frame& F, std::vector<MapPoint*>& vpMapPointMatches);
+    int SearchByBoW(KeyFrame* pKF1, KeyFrame* pKF2, std::vector<MapPoint*>& vpMatches12);
+    void ComputeThreeMaxima(std::vector<int>* histo, const int L, int& ind1, int& ind2, int& ind3);
+    static const int TH_LOW;
+    static const int TH_HIGH;
+    static const int HISTO_LENGTH;
+    float mfNNratio;
+    bool mbCheckOrientation;
+};
+const int ORBmatcher::HISTO_LENGTH = 30;   /* src/ORBmatcher.cc:38 */
 
 #include "_ref/ORBmatcher_constants.inc"
 #include "_ref/ORBmatcher_DescriptorDistance.inc"
 #include "_ref/Frame_ComputeStereoMatches.inc"
+#include "_ref/ORBmatcher_ComputeThreeMaxima.inc"
+#include "_ref/ORBmatcher_SearchByBoW.inc"
 
 /* protected members of the extractor, for the stage-level comparisons */
 struct Probe : ORBextractor {
@@ -230,6 +262,66 @@ int ref_descriptor_distance(const uint8_t* a, const uint8_t* b) {
     std::memcpy(ra, a, 32);
     std::memcpy(rb, b, 32);
     return ORB_SLAM3::ORBmatcher::DescriptorDistance(cv::Mat(1, 32, CV_8UC1, ra, 32), cv::Mat(1, 32, CV_8UC1, rb, 32));
+}
+
+/* ORBmatcher::SearchByBoW(KeyFrame*, Frame&, vpMapPointMatches) (src/ORBmatcher.cc:269-470) and, with kf_kf, SearchByBoW(KeyFrame*,
+ * KeyFrame*, vpMatches12) (:823-963) on plain arrays — the argument list of orc_search_by_bow.  has_map_point[i]: 0 = NULL, 1 = a
+ * good map point, 2 = a bad one (isBad()).  match_out: kf_kf = 0: per frame row the keyframe row whose map point was assigned, or -1;
+ * kf_kf = 1: per keyframe-1 row the keyframe-2 row, or -1.  Returns nmatches. */
+int ref_search_by_bow(const uint8_t* desc_kf, const orc_keypoint* kps_kf, int n_kf, const int32_t* nodes_kf, const int32_t* starts_kf, const int32_t* feats_kf,
+                      int nfv_kf, const uint8_t* has_map_point, const uint8_t* desc_f, const orc_keypoint* kps_f, int n_f, const int32_t* nodes_f,
+                      const int32_t* starts_f, const int32_t* feats_f, int nfv_f, const uint8_t* has_map_point_f, int n_left_f, float nnratio,
+                      int check_orientation, int kf_kf, int32_t* match_out) {
+    using namespace ORB_SLAM3;
+    ArenaScope scope;
+    auto fill_fv = [](DBoW2::FeatureVector& fv, const int32_t* nodes, const int32_t* starts, const int32_t* feats, int n) {
+        for (int e = 0; e < n; e++) {
+            std::vector<unsigned int> v(feats + starts[e], feats + starts[e + 1]);
+            fv.insert(fv.end(), std::make_pair((DBoW2::NodeId)nodes[e], v));
+        }
+    };
+    auto keys_of = [](const orc_keypoint* k, int n) {
+        std::vector<cv::KeyPoint> v(n);
+        if (n) std::memcpy((void*)v.data(), k, sizeof(orc_keypoint) * n);
+        return v;
+    };
+    std::vector<MapPoint> store(n_kf + n_f);
+    auto points_of = [&](const uint8_t* has, int n, int base) {
+        std::vector<MapPoint*> v(n, nullptr);
+        for (int i = 0; i < n; i++)
+            if (has && has[i]) { store[base + i].bad = has[i] == 2; v[i] = &store[base + i]; }
+        return v;
+    };
+    KeyFrame kf;
+    kf.mDescriptors = cv::Mat(n_kf, 32, CV_8UC1, (void*)desc_kf, 32);
+    kf.mvKeysUn = kf.mvKeys = keys_of(kps_kf, n_kf);
+    kf.mvpMapPoints = points_of(has_map_point, n_kf, 0);
+    fill_fv(kf.mFeatVec, nodes_kf, starts_kf, feats_kf, nfv_kf);
+    ORBmatcher matcher(nnratio, check_orientation != 0);
+    std::vector<MapPoint*> out;
+    int nm;
+    if (!kf_kf) {
+        Frame F;
+        F.N = n_f;
+        F.Nleft = n_left_f;
+        static int rig_marker;
+        if (n_left_f >= 0) F.mpCamera2 = &rig_marker;   /* a fisheye rig: the frame has a second camera */
+        F.mDescriptors = cv::Mat(n_f, 32, CV_8UC1, (void*)desc_f, 32);
+        if (n_left_f < 0) F.mvKeysUn = F.mvKeys = keys_of(kps_f, n_f);
+        else { F.mvKeys = keys_of(kps_f, n_left_f); F.mvKeysRight = keys_of(kps_f + n_left_f, n_f - n_left_f); }
+        fill_fv(F.mFeatVec, nodes_f, starts_f, feats_f, nfv_f);
+        nm = matcher.SearchByBoW(&kf, F, out);
+        for (int i = 0; i < n_f; i++) match_out[i] = out[i] ? (int32_t)(out[i] - &store[0]) : -1;
+    } else {
+        KeyFrame kf2;
+        kf2.mDescriptors = cv::Mat(n_f, 32, CV_8UC1, (void*)desc_f, 32);
+        kf2.mvKeysUn = kf2.mvKeys = keys_of(kps_f, n_f);
+        kf2.mvpMapPoints = points_of(has_map_point_f, n_f, n_kf);
+        fill_fv(kf2.mFeatVec, nodes_f, starts_f, feats_f, nfv_f);
+        nm = matcher.SearchByBoW(&kf, &kf2, out);
+        for (int i = 0; i < n_kf; i++) match_out[i] = out[i] ? (int32_t)(out[i] - &store[n_kf]) : -1;
+    }
+    return nm;
 }
 
 int ref_th_low(void) { return ORB_SLAM3::ORBmatcher::TH_LOW; }

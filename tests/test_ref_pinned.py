@@ -212,3 +212,48 @@ def test_bow_oracle_equals_vendored_dbow2(tmp_path, k, L, scoring, weighting, le
             assert np.array_equal(got["feat_vec"][node], want["feat_vec"][node]), (n, node)
         if n == 1200:
             assert len(want["bow_words"]) > 20
+
+
+def _test_bow_helpers():
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("test_bow_helpers", os.path.join(os.path.dirname(os.path.abspath(__file__)), "test_bow.py"))
+    tb = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(tb)
+    return tb
+
+
+@pytest.mark.parametrize("k,L,levelsup,seed,n_kf,n_f", [(4, 3, 1, 21, 400, 450), (10, 3, 2, 22, 800, 700), (3, 4, 3, 23, 600, 600), (10, 4, 2, 24, 1200, 1300),
+                                                     (2, 2, 1, 25, 500, 500)])
+def test_search_by_bow_equals_reference(k, L, levelsup, seed, n_kf, n_f):
+    """ORBmatcher::SearchByBoW, both overloads (src/ORBmatcher.cc:269-470, 823-963) with ComputeThreeMaxima (:2545-2586): the bodies cut
+    out of the reference's file and compiled (oracle/Makefile) against the oracle's restatement — node gating, the serial
+    `already matched` rule, TH_LOW `<=` vs `<`, the ratio test, the fisheye-rig branch with its right-camera best, the rotation
+    histogram.  Identical match arrays and counts."""
+    tb = _test_bow_helpers()
+    rows = tb.make_vocabulary(seed, k, L)
+    voc = O.OracleVocabulary(k, L, 0, 0, *rows)
+    d_kf, k_kf, has_mp, d_f, k_f = tb.make_pair(seed, rows, n_kf, n_f)
+    fv_kf, fv_f = voc.transform(d_kf, levelsup)["feat_vec"], voc.transform(d_f, levelsup)["feat_vec"]
+    rng = np.random.RandomState(seed)
+    has_mp_f = (rng.uniform(size=n_f) < 0.7).astype(np.uint8)
+    total = 0
+    for ori in (True, False):
+        for ratio in (0.7, 0.9):
+            got, _, nm = O.search_by_bow(d_kf, k_kf, fv_kf, has_mp, d_f, k_f, fv_f, 50, ratio, ori)
+            want, wnm = Rf.search_by_bow(d_kf, k_kf, fv_kf, has_mp, d_f, k_f, fv_f, ratio, ori)
+            assert np.array_equal(got, want) and nm == wnm, ("kf-frame", ori, ratio)
+            total += nm
+            got, _, nm = O.search_by_bow(d_kf, k_kf, fv_kf, has_mp, d_f, k_f, fv_f, 50, ratio, ori, n_left_f=n_f // 2)
+            want, wnm = Rf.search_by_bow(d_kf, k_kf, fv_kf, has_mp, d_f, k_f, fv_f, ratio, ori, n_left_f=n_f // 2)
+            assert np.array_equal(got, want) and nm == wnm, ("fisheye rig", ori, ratio)
+            _, kf_out, nm = O.search_by_bow(d_kf, k_kf, fv_kf, has_mp, d_f, k_f, fv_f, 50, ratio, ori, kf_kf=True, has_map_point_f=has_mp_f)
+            want, wnm = Rf.search_by_bow(d_kf, k_kf, fv_kf, has_mp, d_f, k_f, fv_f, ratio, ori, kf_kf=True, has_map_point_f=has_mp_f)
+            got = np.where(kf_out["accepted"] == 1, kf_out["idx"], -1)
+            assert np.array_equal(got, want) and nm == wnm, ("kf-kf", ori, ratio)
+    assert total > 100
+    # bad map points are skipped like missing ones (pMP->isBad(), :303-304)
+    bad = has_mp.copy()
+    bad[::3] = np.where(bad[::3] == 1, 2, 0)
+    got, _, nm = O.search_by_bow(d_kf, k_kf, fv_kf, (bad == 1).astype(np.uint8), d_f, k_f, fv_f, 50, 0.7, True)
+    want, wnm = Rf.search_by_bow(d_kf, k_kf, fv_kf, bad, d_f, k_f, fv_f, 0.7, True)
+    assert np.array_equal(got, want) and nm == wnm
