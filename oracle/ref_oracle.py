@@ -49,6 +49,7 @@ def lib(fma=False):
     L.ref_stereo.argtypes = par + [vp, vp, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, vp, vp, i32p, vp, vp, i32p, C.c_int, vp, vp]
     L.ref_descriptor_distance.argtypes = [vp, vp]
     L.ref_search_by_bow.argtypes = [vp, vp, C.c_int, vp, vp, vp, C.c_int, vp, vp, vp, C.c_int, vp, vp, vp, C.c_int, vp, C.c_int, C.c_float, C.c_int, C.c_int, vp]
+    L.ref_search_by_projection.argtypes = [vp, vp, C.c_int, C.c_int, vp, vp, vp, vp, vp, vp, C.c_int, C.c_int] + [vp] * 12 + [C.c_float, C.c_float, vp]
     _libs[fma] = L
     return L
 
@@ -142,6 +143,27 @@ def search_by_bow(desc_kf, kps_kf, fv_kf, has_map_point, desc_f, kps_f, fv_f, nn
                                  desc_f.shape[0], _ptr(nb), _ptr(sb), _ptr(fb), len(nb), _ptr(mpf) if mpf is not None else None, int(n_left_f), nnratio,
                                  int(check_orientation), int(kf_kf), _ptr(out))
     return out[:(desc_kf.shape[0] if kf_kf else desc_f.shape[0])], nm
+
+
+def search_by_projection(kps, desc, n_left, u_right, l2r, r2l, taken, grid4, scale_factors, mp, th, nnratio):
+    """The reference's own ORBmatcher::SearchByProjection(Frame&, vpMapPoints, th) on arrays; `mp` is a dict of per-map-point arrays named
+    like the MapPoint fields (in_view, in_view_r, level, level_r, view_cos, view_cos_r, proj_x, proj_y, proj_xr, proj_yr, obs, desc).
+    Returns (owner[n] = map point index per keypoint row, -2 the initial one, -1 none; nmatches)."""
+    kps, desc = np.ascontiguousarray(kps, KP_DTYPE), np.ascontiguousarray(desc, np.uint8)
+    n = kps.shape[0]
+    f = lambda a, t: np.ascontiguousarray(a, t)  # noqa: E731
+    ur = None if u_right is None else f(u_right, np.float32)
+    a_l2r = None if l2r is None else f(l2r, np.int32)
+    a_r2l = None if r2l is None else f(r2l, np.int32)
+    tk, g, sf = f(taken, np.uint8), f(grid4, np.float32), f(scale_factors, np.float32)
+    arrs = [f(mp["in_view"], np.uint8), f(mp["in_view_r"], np.uint8), f(mp["level"], np.int32), f(mp["level_r"], np.int32), f(mp["view_cos"], np.float32),
+            f(mp["view_cos_r"], np.float32), f(mp["proj_x"], np.float32), f(mp["proj_y"], np.float32), f(mp["proj_xr"], np.float32),
+            f(mp["proj_yr"], np.float32), f(mp["obs"], np.int32), f(mp["desc"], np.uint8)]
+    owner = np.zeros(max(n, 1), np.int32)
+    p = lambda a: _ptr(a) if a is not None else None  # noqa: E731
+    nm = lib().ref_search_by_projection(_ptr(kps), _ptr(desc), n, int(n_left), p(ur), p(a_l2r), p(a_r2l), _ptr(tk), _ptr(g), _ptr(sf), len(sf), len(arrs[0]),
+                                        *[_ptr(a) for a in arrs], float(th), float(nnratio), _ptr(owner))
+    return owner[:n], nm
 
 
 def set_arena(on, fma=False):

@@ -103,7 +103,18 @@ class MapPoint {
 public:
     bool bad = false;
     bool isBad() { return bad; }
+    /* the tracking fields SearchByProjection reads (include/MapPoint.h:126-137) */
+    bool mbTrackInView = false, mbTrackInViewR = false;
+    float mTrackProjX = 0, mTrackProjY = 0, mTrackDepth = 0, mTrackProjXR = 0, mTrackProjYR = 0, mTrackViewCos = 0, mTrackViewCosR = 0;
+    int mnTrackScaleLevel = 0, mnTrackScaleLevelR = 0;
+    int nObs = 0;
+    cv::Mat mDescriptor;
+    int Observations() { return nObs; }
+    cv::Mat GetDescriptor() { return mDescriptor.clone(); }
 };
+
+#define FRAME_GRID_ROWS 48 /* include/Frame.h:37-38 */
+#define FRAME_GRID_COLS 64
 
 class Frame {
 public:
@@ -118,7 +129,18 @@ public:
     std::vector<float> mvScaleFactors, mvInvScaleFactors;
     DBoW2::FeatureVector mFeatVec;
     void* mpCamera2 = nullptr;   /* GeometricCamera*: only tested against NULL by the bodies taken here */
+    /* the grid of include/Frame.h:187-189,232-235,296 and what SearchByProjection touches */
+    std::vector<size_t> GetFeaturesInArea(const float& x, const float& y, const float& r, const int minLevel = -1, const int maxLevel = -1,
+                                          const bool bRight = false) const;
+    bool PosInGrid(const cv::KeyPoint& kp, int& posX, int& posY);
+    void AssignFeaturesToGrid();
+    static float mfGridElementWidthInv, mfGridElementHeightInv, mnMinX, mnMinY;
+    std::vector<std::size_t> mGrid[FRAME_GRID_COLS][FRAME_GRID_ROWS];
+    std::vector<std::size_t> mGridRight[FRAME_GRID_COLS][FRAME_GRID_ROWS];
+    std::vector<MapPoint*> mvpMapPoints;
+    std::vector<int> mvLeftToRightMatch, mvRightToLeftMatch;
 };
+float Frame::mfGridElementWidthInv, Frame::mfGridElementHeightInv, Frame::mnMinX, Frame::mnMinY;
 
 class KeyFrame {
 public:
@@ -137,6 +159,8 @@ public:
     static int DescriptorDistance(const cv::Mat& a, const cv::Mat& b);
     int SearchByBoW(KeyFrame* pKF, Frame& F, std::vector<MapPoint*>& vpMapPointMatches);
     int SearchByBoW(KeyFrame* pKF1, KeyFrame* pKF2, std::vector<MapPoint*>& vpMatches12);
+    int SearchByProjection(Frame& F, const std::vector<MapPoint*>& vpMapPoints, const float th = 3, const bool bFarPoints = false, const float thFarPoints = 50.0f);
+    float RadiusByViewingCos(const float& viewCos);
     void ComputeThreeMaxima(std::vector<int>* histo, const int L, int& ind1, int& ind2, int& ind3);
     static const int TH_LOW;
     static const int TH_HIGH;
@@ -151,6 +175,8 @@ const int ORBmatcher::HISTO_LENGTH = 30;   /* src/ORBmatcher.cc:38 */
 #include "_ref/Frame_ComputeStereoMatches.inc"
 #include "_ref/ORBmatcher_ComputeThreeMaxima.inc"
 #include "_ref/ORBmatcher_SearchByBoW.inc"
+#include "_ref/Frame_grid.inc"
+#include "_ref/ORBmatcher_SearchByProjection.inc"
 
 /* protected members of the extractor, for the stage-level comparisons */
 struct Probe : ORBextractor {
@@ -321,6 +347,55 @@ int ref_search_by_bow(const uint8_t* desc_kf, const orc_keypoint* kps_kf, int n_
         nm = matcher.SearchByBoW(&kf, &kf2, out);
         for (int i = 0; i < n_kf; i++) match_out[i] = out[i] ? (int32_t)(out[i] - &store[n_kf]) : -1;
     }
+    return nm;
+}
+
+/* ORBmatcher::SearchByProjection(Frame&, vpMapPoints, th, bFarPoints = false) (src/ORBmatcher.cc:44-214) on a frame given as arrays, with the
+ * grid built by the reference's own AssignFeaturesToGrid.  kps / desc: n rows (rows >= n_left: the right camera, n_left = -1: none);
+ * l2r [n_left] / r2l [n - n_left]: mvLeftToRightMatch / mvRightToLeftMatch; taken[i] != 0: the row starts with a map point that has
+ * observations.  Map points as arrays of nmp entries (the MapPoint fields of the same names; desc_mp nmp x 32).  grid4 = mnMinX, mnMinY,
+ * mfGridElementWidthInv, mfGridElementHeightInv.  owner[i] = index of the map point row i holds afterwards, -2 = the initial one, -1 = none. */
+int ref_search_by_projection(const orc_keypoint* kps, const uint8_t* desc, int n, int n_left, const float* u_right, const int32_t* l2r, const int32_t* r2l,
+                             const uint8_t* taken, const float* grid4, const float* scale_factors, int nlevels, int nmp, const uint8_t* in_view,
+                             const uint8_t* in_view_r, const int32_t* level, const int32_t* level_r, const float* view_cos, const float* view_cos_r,
+                             const float* proj_x, const float* proj_y, const float* proj_xr, const float* proj_yr, const int32_t* obs, const uint8_t* desc_mp,
+                             float th, float nnratio, int32_t* owner) {
+    using namespace ORB_SLAM3;
+    ArenaScope scope;
+    Frame F;
+    Frame::mnMinX = grid4[0]; Frame::mnMinY = grid4[1]; Frame::mfGridElementWidthInv = grid4[2]; Frame::mfGridElementHeightInv = grid4[3];
+    F.N = n;
+    F.Nleft = n_left;
+    F.mDescriptors = cv::Mat(n, 32, CV_8UC1, (void*)desc, 32);
+    std::vector<cv::KeyPoint> all(n);
+    if (n) std::memcpy((void*)all.data(), kps, sizeof(orc_keypoint) * n);
+    if (n_left < 0) F.mvKeysUn = F.mvKeys = all;
+    else { F.mvKeys.assign(all.begin(), all.begin() + n_left); F.mvKeysRight.assign(all.begin() + n_left, all.end()); }
+    F.mvuRight.assign(n, -1.f);
+    if (u_right) F.mvuRight.assign(u_right, u_right + n);
+    if (n_left >= 0) { F.mvLeftToRightMatch.assign(l2r, l2r + n_left); F.mvRightToLeftMatch.assign(r2l, r2l + (n - n_left)); }
+    F.mvScaleFactors.assign(scale_factors, scale_factors + nlevels);
+    F.AssignFeaturesToGrid();
+    MapPoint initial;
+    initial.nObs = 1;
+    F.mvpMapPoints.assign(n, nullptr);
+    for (int i = 0; i < n; i++)
+        if (taken && taken[i]) F.mvpMapPoints[i] = &initial;
+    std::vector<MapPoint> store(nmp);
+    std::vector<MapPoint*> vp(nmp);
+    for (int i = 0; i < nmp; i++) {
+        MapPoint& m = store[i];
+        m.mbTrackInView = in_view[i]; m.mbTrackInViewR = in_view_r[i];
+        m.mnTrackScaleLevel = level[i]; m.mnTrackScaleLevelR = level_r[i];
+        m.mTrackViewCos = view_cos[i]; m.mTrackViewCosR = view_cos_r[i];
+        m.mTrackProjX = proj_x[i]; m.mTrackProjY = proj_y[i]; m.mTrackProjXR = proj_xr[i]; m.mTrackProjYR = proj_yr[i];
+        m.nObs = obs[i];
+        m.mDescriptor = cv::Mat(1, 32, CV_8UC1, (void*)(desc_mp + (size_t)i * 32), 32);
+        vp[i] = &m;
+    }
+    ORBmatcher matcher(nnratio, true);
+    const int nm = matcher.SearchByProjection(F, vp, th, false, 50.0f);
+    for (int i = 0; i < n; i++) owner[i] = !F.mvpMapPoints[i] ? -1 : F.mvpMapPoints[i] == &initial ? -2 : (int32_t)(F.mvpMapPoints[i] - store.data());
     return nm;
 }
 

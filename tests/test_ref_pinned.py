@@ -257,3 +257,83 @@ def test_search_by_bow_equals_reference(k, L, levelsup, seed, n_kf, n_f):
     got, _, nm = O.search_by_bow(d_kf, k_kf, fv_kf, (bad == 1).astype(np.uint8), d_f, k_f, fv_f, 50, 0.7, True)
     want, wnm = Rf.search_by_bow(d_kf, k_kf, fv_kf, bad, d_f, k_f, fv_f, 0.7, True)
     assert np.array_equal(got, want) and nm == wnm
+
+
+@pytest.mark.parametrize("name,kw", [("mono", dict(seed=31, n=600, nq=700)), ("stereo_gate", dict(seed=32, n=800, nq=900, stereo_gate=True)),
+                                     ("wide", dict(seed=33, n=500, nq=600, th=3.0, crowd=0.5)), ("crowd", dict(seed=34, n=700, nq=900, th=2.0, crowd=0.8)),
+                                     ("fisheye", dict(seed=35, n=900, nq=800, fisheye=True, th=1.0, crowd=0.3))])
+def test_search_by_projection_equals_reference(name, kw):
+    """ORBmatcher::SearchByProjection(Frame&, vpMapPoints, th, ...) (src/ORBmatcher.cc:44-214, Tracking::SearchLocalPoints) with
+    Frame::GetFeaturesInArea / PosInGrid / AssignFeaturesToGrid (src/Frame.cc:380-411, 643-721) — the reference's own bodies, compiled —
+    against the oracle driven through the query list INTEGRATION.md 5a prescribes: every keypoint row must end up with the same map
+    point, and nmatches must agree.  Covers the serial occupancy rule, the uRight gate, the level window, the ratio test with equal
+    levels, the `continue` that skips the right-camera half, and the stereo partner rows of a fisheye rig."""
+    from orb_slam3_detailed_comments_kor_b200.synth import projection_cases as PC
+    f32 = np.float32
+    th = kw.get("th", 1.0)
+    c = PC.make_case(**kw)
+    q = c["queries"].copy()
+    n, n_left = len(c["kps"]), int(c["n_left"][0])
+    scale = np.array([f32(1.2) ** i for i in range(8)], f32)
+    # the overload under test always searches levels [predicted - 1, predicted]; a left half that is skipped takes its right half along
+    open_levels = q["max_level"] < 0
+    q["flags"][open_levels] |= PC.PQ_SKIP
+    q["max_level"][open_levels] = 1; q["min_level"][open_levels] = 0
+    for k in range(1, len(q)):
+        if (q["flags"][k] & PC.PQ_AFTER_LEFT) and (q["flags"][k - 1] & PC.PQ_SKIP):
+            q["flags"][k] |= PC.PQ_SKIP
+    # map points: one per left query, its AFTER_LEFT right query folded in; right-only queries are points seen by the right camera only
+    names = ["in_view", "in_view_r", "level", "level_r", "view_cos", "view_cos_r", "proj_x", "proj_y", "proj_xr", "proj_yr", "obs"]
+    mp = {k: [] for k in names}
+    mp["desc"] = []
+    owner_of_query = np.zeros(len(q), np.int32)
+
+    def cos_of(radius, lvl, with_th):
+        base = [f32(f32(2.5) * f32(th if with_th else 1.0)) * scale[lvl], f32(f32(4.0) * f32(th if with_th else 1.0)) * scale[lvl]]
+        if radius not in base:
+            return None                                  # only for queries that are skipped anyway (asserted below)
+        return 0.999 if radius == base[0] else 0.5
+
+    for k in range(len(q)):
+        fl, lvl = int(q["flags"][k]), int(q["max_level"][k])
+        if fl & PC.PQ_AFTER_LEFT:                       # the right-camera half of the previous map point
+            i = len(mp["obs"]) - 1
+            mp["in_view_r"][i] = 0 if fl & PC.PQ_SKIP else 1
+            vc = cos_of(q["radius"][k], lvl, False)
+            assert vc is not None or fl & PC.PQ_SKIP
+            mp["level_r"][i], mp["view_cos_r"][i], mp["proj_xr"][i], mp["proj_yr"][i] = lvl, vc or 0.0, q["x"][k], q["y"][k]
+            owner_of_query[k] = i
+            continue
+        right_only = bool(fl & PC.PQ_RIGHT)
+        seen = 0 if fl & PC.PQ_SKIP else 1
+        mp["in_view"].append(0 if right_only else seen); mp["in_view_r"].append(seen if right_only else 0)
+        mp["level"].append(lvl); mp["level_r"].append(lvl if right_only else -1)
+        vc = cos_of(q["radius"][k], lvl, not right_only)
+        assert vc is not None or fl & PC.PQ_SKIP
+        mp["view_cos"].append((vc or 0.0) if not right_only else 0.0)
+        mp["view_cos_r"].append((vc or 0.0) if right_only else 0.0)
+        mp["proj_x"].append(q["x"][k]); mp["proj_y"].append(q["y"][k])
+        mp["proj_xr"].append(q["x"][k] if right_only else q["xr"][k]); mp["proj_yr"].append(q["y"][k])
+        mp["obs"].append(1 if fl & PC.PQ_BLOCKS else 0)
+        mp["desc"].append(c["qdesc"][k])
+        owner_of_query[k] = len(mp["obs"]) - 1
+    mp["desc"] = np.stack(mp["desc"])
+    partner = c.get("partner")
+    l2r = r2l = None
+    if n_left >= 0:
+        l2r = np.where(partner[:n_left] >= 0, partner[:n_left] - n_left, -1).astype(np.int32)
+        r2l = partner[n_left:].astype(np.int32)
+    # the oracle, through the query list
+    pm, taken_after, nm = O.search_by_projection(c["kps"], c["desc"], q, c["qdesc"], c["grid"], n_left=n_left, u_right=c.get("u_right"), partner=partner,
+                                                 taken=c["taken"], th_high=100, nnratio=float(c["nnratio"][0]))
+    want = np.where(c["taken"] != 0, -2, -1).astype(np.int32)
+    for k in range(len(q)):
+        if pm["accepted"][k]:
+            row = int(pm["best_idx"][k])
+            want[row] = owner_of_query[k]
+            if n_left >= 0 and partner[row] >= 0:
+                want[partner[row]] = owner_of_query[k]
+    got, rnm = Rf.search_by_projection(c["kps"], c["desc"], n_left, c.get("u_right"), l2r, r2l, c["taken"], c["grid"], scale, mp, th, float(c["nnratio"][0]))
+    assert np.array_equal(got, want), "%s: %d rows differ" % (name, int((got != want).sum()))
+    assert rnm == nm and nm > 50
+    assert set(np.unique(pm["status"])) >= {0, 1, 3, 4} or name != "wide"       # empty window / accepted / ratio-rejected / skipped all occur
