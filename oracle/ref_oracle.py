@@ -49,6 +49,7 @@ def lib(fma=False):
     L.ref_stereo.argtypes = par + [vp, vp, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, vp, vp, i32p, vp, vp, i32p, C.c_int, vp, vp]
     L.ref_descriptor_distance.argtypes = [vp, vp]
     L.ref_search_by_bow.argtypes = [vp, vp, C.c_int, vp, vp, vp, C.c_int, vp, vp, vp, C.c_int, vp, vp, vp, C.c_int, vp, C.c_int, C.c_float, C.c_int, C.c_int, vp]
+    L.ref_distinctive_descriptor.argtypes = [vp, C.c_int, vp]
     L.ref_search_by_projection.argtypes = [vp, vp, C.c_int, C.c_int, vp, vp, vp, vp, vp, vp, C.c_int, C.c_int] + [vp] * 12 + [C.c_float, C.c_float, vp]
     _libs[fma] = L
     return L
@@ -164,6 +165,13 @@ def search_by_projection(kps, desc, n_left, u_right, l2r, r2l, taken, grid4, sca
     nm = lib().ref_search_by_projection(_ptr(kps), _ptr(desc), n, int(n_left), p(ur), p(a_l2r), p(a_r2l), _ptr(tk), _ptr(g), _ptr(sf), len(sf), len(arrs[0]),
                                         *[_ptr(a) for a in arrs], float(th), float(nnratio), _ptr(owner))
     return owner[:n], nm
+
+
+def distinctive_descriptor(desc, bad_kf=None):
+    """The reference's own MapPoint::ComputeDistinctiveDescriptors for one map point: row of `desc` it selects (-1: none)."""
+    desc = np.ascontiguousarray(desc, np.uint8)
+    bad = None if bad_kf is None else np.ascontiguousarray(bad_kf, np.uint8)
+    return lib().ref_distinctive_descriptor(_ptr(desc), desc.shape[0], _ptr(bad) if bad is not None else None)
 
 
 def set_arena(on, fma=False):

@@ -1,13 +1,16 @@
 /* ref_shim.cpp — C entry points around the REFERENCE'S OWN code, compiled where it lies.  TEST INFRASTRUCTURE ONLY.
  *
  * oracle/Makefile (target _ref/liborb_ref.so) compiles /root/reference/src/ORBextractor.cc unmodified against
- * oracle/refstub/ (see cvstub.hpp), and cuts two function bodies out of files that cannot be compiled whole
- * (they pull in Eigen, Sophus, g2o, DBoW2, ...):
- *     /root/reference/src/Frame.cc       Frame::ComputeStereoMatches          -> _ref/Frame_ComputeStereoMatches.inc
- *     /root/reference/src/ORBmatcher.cc  ORBmatcher::DescriptorDistance, TH_* -> _ref/ORBmatcher_*.inc
- * Those generated files live only under oracle/_ref/ (git-ignored); no reference source is stored in this repository.
- * The `Frame` and `ORBmatcher` classes below declare just the members those bodies name (include/Frame.h,
- * include/ORBmatcher.h:42,95-96).
+ * oracle/refstub/ (see cvstub.hpp), and cuts function bodies out of files that cannot be compiled whole
+ * (they pull in Eigen, Sophus, g2o, ...; src/ORBmatcher.cc also stops at a syntax error on line 2226):
+ *     src/Frame.cc       Frame::ComputeStereoMatches, GetFeaturesInArea, PosInGrid, AssignFeaturesToGrid
+ *     src/ORBmatcher.cc  DescriptorDistance, TH_LOW / TH_HIGH, SearchByBoW (both overloads), ComputeThreeMaxima,
+ *                        SearchByProjection(Frame&, vpMapPoints, th, ...) with RadiusByViewingCos
+ *     src/MapPoint.cc    MapPoint::ComputeDistinctiveDescriptors
+ * into _ref/*.inc, which live only under oracle/_ref/ (git-ignored); no reference source is stored in this repository.
+ * The `Frame`, `KeyFrame`, `MapPoint` and `ORBmatcher` classes below declare just the members those bodies name
+ * (include/Frame.h, include/KeyFrame.h, include/MapPoint.h, include/ORBmatcher.h); DBoW2::FeatureVector is the
+ * reference's own (Thirdparty/DBoW2).
  *
  * Allocation: every `new` inside a ref_* call is served from a per-thread bump arena and `delete` is a no-op, so heap
  * addresses grow with creation order.  DistributeOctTree sorts pair<size, ExtractorNode*> (src/ORBextractor.cc:682):
@@ -18,7 +21,10 @@
 #include <sys/mman.h>
 
 #include <atomic>
+#include <map>
+#include <mutex>
 #include <new>
+#include <tuple>
 
 #include "refstub/cvstub.hpp"
 #include "FeatureVector.h" /* the reference's vendored DBoW2 (Thirdparty/DBoW2/DBoW2): the real FeatureVector type */
@@ -94,15 +100,21 @@ void operator delete[](void* p) noexcept { arena_delete(p); }
 void operator delete(void* p, size_t) noexcept { arena_delete(p); }
 void operator delete[](void* p, size_t) noexcept { arena_delete(p); }
 
-/* ---- the two function bodies taken from Frame.cc / ORBmatcher.cc ------------------------------------------------- */
+/* ---- the function bodies taken from Frame.cc / ORBmatcher.cc / MapPoint.cc ----------------------------------------- */
 using namespace std;
 namespace ORB_SLAM3 {
 
 /* only what the cut-out bodies name: include/MapPoint.h (isBad), include/KeyFrame.h and include/Frame.h (the members below) */
+class KeyFrame;
 class MapPoint {
 public:
     bool bad = false;
     bool isBad() { return bad; }
+    /* MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:349-423) and the members it reads (include/MapPoint.h) */
+    void ComputeDistinctiveDescriptors();
+    std::map<KeyFrame*, std::tuple<int, int>> mObservations;
+    std::mutex mMutexFeatures;
+    bool mbBad = false;
     /* the tracking fields SearchByProjection reads (include/MapPoint.h:126-137) */
     bool mbTrackInView = false, mbTrackInViewR = false;
     float mTrackProjX = 0, mTrackProjY = 0, mTrackDepth = 0, mTrackProjXR = 0, mTrackProjYR = 0, mTrackViewCos = 0, mTrackViewCosR = 0;
@@ -151,6 +163,8 @@ public:
     int NLeft = -1;
     std::vector<cv::KeyPoint> mvKeys, mvKeysRight, mvKeysUn;
     void* mpCamera2 = nullptr;
+    bool mbBadKF = false;
+    bool isBad() { return mbBadKF; }
 };
 
 class ORBmatcher {
@@ -176,6 +190,7 @@ const int ORBmatcher::HISTO_LENGTH = 30;   /* src/ORBmatcher.cc:38 */
 #include "_ref/ORBmatcher_ComputeThreeMaxima.inc"
 #include "_ref/ORBmatcher_SearchByBoW.inc"
 #include "_ref/Frame_grid.inc"
+#include "_ref/MapPoint_ComputeDistinctiveDescriptors.inc"
 #include "_ref/ORBmatcher_SearchByProjection.inc"
 
 /* protected members of the extractor, for the stage-level comparisons */
@@ -397,6 +412,25 @@ int ref_search_by_projection(const orc_keypoint* kps, const uint8_t* desc, int n
     const int nm = matcher.SearchByProjection(F, vp, th, false, 50.0f);
     for (int i = 0; i < n; i++) owner[i] = !F.mvpMapPoints[i] ? -1 : F.mvpMapPoints[i] == &initial ? -2 : (int32_t)(F.mvpMapPoints[i] - store.data());
     return nm;
+}
+
+/* MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:349-423) for one map point observed in n keyframes (one descriptor row each;
+ * bad_kf[i] != 0: that keyframe isBad()).  The observation map is ordered by keyframe address; the keyframes sit in one array, so that
+ * order is the row order.  Returns the row of `desc` whose copy becomes mDescriptor, or -1 when nothing is selected. */
+int ref_distinctive_descriptor(const uint8_t* desc, int n, const uint8_t* bad_kf) {
+    using namespace ORB_SLAM3;
+    std::vector<KeyFrame> kfs(n);
+    MapPoint mp;
+    for (int i = 0; i < n; i++) {
+        kfs[i].mDescriptors = cv::Mat(1, 32, CV_8UC1, (void*)(desc + (size_t)i * 32), 32);
+        kfs[i].mbBadKF = bad_kf && bad_kf[i];
+        mp.mObservations[&kfs[i]] = std::make_tuple(0, -1);
+    }
+    mp.ComputeDistinctiveDescriptors();
+    if (mp.mDescriptor.empty()) return -1;
+    for (int i = 0; i < n; i++)
+        if (!(bad_kf && bad_kf[i]) && std::memcmp(mp.mDescriptor.data, desc + (size_t)i * 32, 32) == 0) return i;   /* first equal row */
+    return -1;
 }
 
 int ref_th_low(void) { return ORB_SLAM3::ORBmatcher::TH_LOW; }

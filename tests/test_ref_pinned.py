@@ -337,3 +337,32 @@ def test_search_by_projection_equals_reference(name, kw):
     assert np.array_equal(got, want), "%s: %d rows differ" % (name, int((got != want).sum()))
     assert rnm == nm and nm > 50
     assert set(np.unique(pm["status"])) >= {0, 1, 3, 4} or name != "wide"       # empty window / accepted / ratio-rejected / skipped all occur
+
+
+def test_distinctive_descriptors_equal_reference():
+    """MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:349-423), the reference's body compiled: for map points with 1 .. 60
+    observations (clusters, exact duplicates, outliers) the oracle selects the same row."""
+    rng = np.random.RandomState(8)
+    descs, offsets = [], [0]
+    for p in range(300):
+        n = int(rng.randint(1, 61))
+        base = rng.randint(0, 256, 32).astype(np.uint8)
+        rows = np.repeat(base[None], n, 0)
+        for i in range(n):
+            for b in rng.choice(256, size=int(rng.randint(0, 40)) if rng.uniform() < 0.85 else 128, replace=False):
+                rows[i, b >> 3] ^= np.uint8(1 << (b & 7))
+        if n > 3 and p % 4 == 0:
+            rows[n - 1] = rows[1]                           # duplicate rows: equal medians, the first one wins
+        descs.append(rows)
+        offsets.append(offsets[-1] + n)
+    allrows = np.concatenate(descs)
+    idx, med = O.distinctive_descriptors(allrows, np.array(offsets, np.int32))
+    for p, rows in enumerate(descs):
+        want = Rf.distinctive_descriptor(rows)
+        assert np.array_equal(rows[idx[p]], rows[want]) and idx[p] == want, p
+    # observations in bad keyframes do not take part (:365)
+    rows = descs[7]
+    bad = np.zeros(len(rows), np.uint8); bad[::2] = 1
+    keep = np.nonzero(bad == 0)[0]
+    sub_idx, _ = O.distinctive_descriptors(rows[keep], np.array([0, len(keep)], np.int32))
+    assert keep[sub_idx[0]] == Rf.distinctive_descriptor(rows, bad)
