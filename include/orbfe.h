@@ -183,7 +183,9 @@ int orbfe_matcher_set_db_device(orbfe_matcher* m, const uint8_t* d_db, int64_t r
  * `best1 < th` (KF-KF variant) instead of `best1 <= th`. */
 int orbfe_matcher_top2(orbfe_matcher* m, const uint8_t* h_queries, int nq, int th, float ratio, int strict_lt,
                        orbfe_match* h_out);
-/* Device queries in, device results out, asynchronous on `stream`. */
+/* Device queries in, device results out, asynchronous on `stream` (NULL = the object's stream).  The per-slice scratch belongs to the
+ * object: one search per matcher may be in flight at a time — calls on different streams of the same matcher must be ordered by the
+ * caller (events), or use one matcher per stream. */
 int orbfe_matcher_top2_device(orbfe_matcher* m, const uint8_t* d_queries, int nq, int th, float ratio,
                               int strict_lt, orbfe_match* d_out, void* stream);
 /* Merge step of the sharded database: d_parts holds nshards x nq orbfe_match records (one
