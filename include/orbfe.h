@@ -329,6 +329,17 @@ int orbfe_search_by_bow(int device, const uint8_t* desc_kf, const orbfe_keypoint
                         int n_left_f, int th_low, float nnratio, int check_orientation, int kf_kf, int32_t* match_f, orbfe_match* kf_out,
                         int* nmatches);
 
+/* Two-camera (fisheye) rigs in SearchForTriangulation (src/ORBmatcher.cc:990-1003, 1102-1132): when both keyframes have an mpCamera2, rows
+ * >= NLeft of a keyframe are right-camera keypoints (mvKeysRight), no keypoint counts as stereo, the epipole test is off, and the geometric
+ * test is KannalaBrandt8::epipolarConstrain = TriangulateMatches(...) > 0.0001f (src/CameraModels/KannalaBrandt8.cpp:234-237) with the cameras
+ * and the relative pose of the two sides: cam = mvParameters of pKF1->mpCamera, pKF1->mpCamera2, pKF2->mpCamera, pKF2->mpCamera2; R / t =
+ * Rll, Rlr, Rrl, Rrr and tll, tlr, trl, trr exactly as the reference computes them (row-major).  Pass one per pair (device entry) or one
+ * (host entry) in the last argument; NULL = pinhole keyframes, F12 / epipole are then used as before (they are ignored with a rig). */
+typedef struct {
+    float cam[4][8];
+    float R[4][9], t[4][3];
+    int32_t n_left_1, n_left_2;
+} orbfe_triangulation_rig;
 /* Replaces ORBmatcher::SearchForTriangulation(KeyFrame *pKF1, KeyFrame *pKF2, cv::Mat F12, vMatchedPairs, bOnlyStereo, bCoarse)
  * (src/ORBmatcher.cc:965-1206; LocalMapping::CreateNewMapPoints) for pinhole keyframes without a second camera, for batches of
  * keyframe pairs in the strided layout of orbfe_search_by_bow_device: features of keyframe 1 without a map point against the features
@@ -342,14 +353,15 @@ int orbfe_search_for_triangulation_device(int device, int npairs, int max_featur
                                           const orbfe_keypoint* d_kps, const float* d_u_right, int row_stride, const int32_t* d_fv_nodes,
                                           const int32_t* d_fv_starts, const int32_t* d_fv_feats, const int32_t* d_fv_count, const uint8_t* d_has_map_point,
                                           const float* d_f12, const float* d_epipole, const float* d_scale_factors, const float* d_level_sigma2, int th_low,
-                                          int only_stereo, int coarse, int check_orientation, int32_t* d_match_12, int32_t* d_nmatches, void* stream);
+                                          int only_stereo, int coarse, int check_orientation, int32_t* d_match_12, int32_t* d_nmatches, void* stream,
+                                          const orbfe_triangulation_rig* d_rigs);
 /* One pair over host memory (scale_factors / level_sigma2: nlevels entries). */
 int orbfe_search_for_triangulation(int device, const uint8_t* desc_1, const orbfe_keypoint* kps_1, const float* u_right_1, const uint8_t* has_map_point_1, int n_1,
                                    const int32_t* fv_nodes_1, const int32_t* fv_starts_1, const int32_t* fv_feats_1, int nfv_1, const uint8_t* desc_2,
                                    const orbfe_keypoint* kps_2, const float* u_right_2, const uint8_t* has_map_point_2, int n_2, const int32_t* fv_nodes_2,
                                    const int32_t* fv_starts_2, const int32_t* fv_feats_2, int nfv_2, const float* f12, const float* epipole,
                                    const float* scale_factors, const float* level_sigma2, int nlevels, int th_low, int only_stereo, int coarse,
-                                   int check_orientation, int32_t* match_12, int* nmatches);
+                                   int check_orientation, int32_t* match_12, int* nmatches, const orbfe_triangulation_rig* rig);
 
 /* Replaces the computation of MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:349-423) for many map points at once
  * (SURVEY.md §8f N4): map point p owns the descriptor rows [offsets[p], offsets[p+1]) (the rows of vDescriptors, :352-384);

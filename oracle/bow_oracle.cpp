@@ -216,6 +216,11 @@ int orc_search_by_bow(const uint8_t* desc_kf, const orc_keypoint* kps_kf, int n_
     return nmatches;
 }
 
+/* layout of orbfe_triangulation_rig (include/orbfe.h): cameras 1 left / right, 2 left / right; poses ll, lr, rl, rr */
+typedef struct { float cam[4][8]; float R[4][9], t[4][3]; int32_t n_left_1, n_left_2; } orc_triangulation_rig;
+void orc_kb8_triangulate_matches(const float* cam1, const float* cam2, const float* R12, const float* t12, const float* uv1, const float* uv2,
+                                 const float* sigma1, const float* sigma2, int n, float* depth, float* p3d);   /* triangulate_oracle.cpp */
+
 /* ORBmatcher::SearchForTriangulation(pKF1, pKF2, F12, vMatchedPairs, bOnlyStereo, bCoarse), src/ORBmatcher.cc:965-1206, for pinhole
  * keyframes without a second camera, with Pinhole::epipolarConstrain (src/CameraModels/Pinhole.cpp:135-157) evaluated on the given
  * F12 (row-major 3x3).  match_12[i] = vMatches12[i].  Returns nmatches. */
@@ -224,7 +229,7 @@ int orc_search_for_triangulation(const uint8_t* desc_1, const orc_keypoint* kps_
                                  const orc_keypoint* kps_2, const float* u_right_2, const uint8_t* has_mp_2, int n_2, const int32_t* nodes_2,
                                  const int32_t* starts_2, const int32_t* feats_2, int nfv_2, const float* F12, const float* ep,
                                  const float* scale_factors, const float* level_sigma2, int th_low, int only_stereo, int coarse,
-                                 int check_orientation, int32_t* match_12) {
+                                 int check_orientation, int32_t* match_12, const orc_triangulation_rig* rig) {
     const int HISTO_LENGTH = 30;
     std::vector<bool> vbMatched2(n_2, false);   /* declared and tested by the reference, never set */
     for (int i = 0; i < n_1; i++) match_12[i] = -1;
@@ -237,7 +242,7 @@ int orc_search_for_triangulation(const uint8_t* desc_1, const orc_keypoint* kps_
             for (int i1 = starts_1[f1it]; i1 < starts_1[f1it + 1]; i1++) {
                 const int idx1 = feats_1[i1];
                 if (has_mp_1 && has_mp_1[idx1]) continue;
-                const bool bStereo1 = u_right_1 && u_right_1[idx1] >= 0;
+                const bool bStereo1 = !rig && u_right_1 && u_right_1[idx1] >= 0;   /* !pKF1->mpCamera2 && mvuRight[idx1] >= 0 */
                 if (only_stereo && !bStereo1) continue;
                 const orc_keypoint& kp1 = kps_1[idx1];
                 const uint8_t* d1 = desc_1 + (size_t)idx1 * 32;
@@ -245,17 +250,24 @@ int orc_search_for_triangulation(const uint8_t* desc_1, const orc_keypoint* kps_
                 for (int i2 = starts_2[f2it]; i2 < starts_2[f2it + 1]; i2++) {
                     const int idx2 = feats_2[i2];
                     if (vbMatched2[idx2] || (has_mp_2 && has_mp_2[idx2])) continue;
-                    const bool bStereo2 = u_right_2 && u_right_2[idx2] >= 0;
+                    const bool bStereo2 = !rig && u_right_2 && u_right_2[idx2] >= 0;
                     if (only_stereo && !bStereo2) continue;
                     const int dist = orc_descriptor_distance(d1, desc_2 + (size_t)idx2 * 32);
                     if (dist > th_low || dist > bestDist) continue;
                     const orc_keypoint& kp2 = kps_2[idx2];
-                    if (!bStereo1 && !bStereo2) {
+                    if (!bStereo1 && !bStereo2 && !rig) {
                         const float distex = ep[0] - kp2.x, distey = ep[1] - kp2.y;
                         if (distex * distex + distey * distey < 100 * scale_factors[kp2.octave]) continue;
                     }
                     bool ok = coarse != 0;
-                    if (!ok) {   /* Pinhole::epipolarConstrain */
+                    if (!ok && rig) {   /* two-camera rig (:1102-1132): KannalaBrandt8::epipolarConstrain = TriangulateMatches(...) > 0.0001f */
+                        const int r1 = idx1 >= rig->n_left_1 ? 1 : 0, r2 = idx2 >= rig->n_left_2 ? 1 : 0, combo = 2 * r1 + r2;
+                        const float uv1[2] = {kp1.x, kp1.y}, uv2[2] = {kp2.x, kp2.y};
+                        float depth = -1.f, p3d[3];
+                        orc_kb8_triangulate_matches(rig->cam[r1], rig->cam[2 + r2], rig->R[combo], rig->t[combo], uv1, uv2, &level_sigma2[kp1.octave],
+                                                    &level_sigma2[kp2.octave], 1, &depth, p3d);
+                        ok = depth > 0.0001f;
+                    } else if (!ok) {   /* Pinhole::epipolarConstrain */
                         const float a = kp1.x * F12[0] + kp1.y * F12[3] + F12[6];
                         const float b = kp1.x * F12[1] + kp1.y * F12[4] + F12[7];
                         const float c = kp1.x * F12[2] + kp1.y * F12[5] + F12[8];

@@ -71,7 +71,7 @@ def lib():
     L.orc_search_by_bow.argtypes = [vp, vp, C.c_int, vp, vp, vp, C.c_int, vp, vp, vp, C.c_int, vp, vp, vp, C.c_int, vp, C.c_int, C.c_int, C.c_float, C.c_int, C.c_int, vp, vp]
     L.orc_search_by_bow.restype = C.c_int
     L.orc_search_for_triangulation.argtypes = [vp, vp, vp, vp, C.c_int, vp, vp, vp, C.c_int, vp, vp, vp, vp, C.c_int, vp, vp, vp, C.c_int, vp, vp, vp, vp,
-                                               C.c_int, C.c_int, C.c_int, C.c_int, vp]
+                                               C.c_int, C.c_int, C.c_int, C.c_int, vp, vp]
     L.orc_search_for_triangulation.restype = C.c_int
     L.orc_distinctive_descriptors.argtypes = [vp, vp, C.c_int, vp, vp]
     L.orc_search_by_projection.argtypes = [vp, vp, C.c_int, C.c_int, vp, vp, vp, vp, vp, vp, C.c_int, C.c_int, C.c_float, C.c_int, vp, vp]
@@ -296,8 +296,9 @@ def search_by_bow(desc_kf, kps_kf, fv_kf, has_map_point, desc_f, kps_f, fv_f, th
 
 
 def search_for_triangulation(desc_1, kps_1, u_right_1, has_mp_1, fv_1, desc_2, kps_2, u_right_2, has_mp_2, fv_2, f12, epipole, scale_factors,
-                             level_sigma2, th_low=50, only_stereo=False, coarse=False, check_orientation=True):
-    """ORBmatcher::SearchForTriangulation (pinhole, no second camera).  Returns (vMatches12, nmatches)."""
+                             level_sigma2, th_low=50, only_stereo=False, coarse=False, check_orientation=True, rig=None):
+    """ORBmatcher::SearchForTriangulation; rig = the bytes of an orbfe_triangulation_rig for two-camera keyframes, None for pinhole ones.
+    Returns (vMatches12, nmatches)."""
     c = lambda a, t: None if a is None else np.ascontiguousarray(a, t)  # noqa: E731
     d1, d2, k1, k2 = c(desc_1, np.uint8), c(desc_2, np.uint8), c(kps_1, KP_DTYPE), c(kps_2, KP_DTYPE)
     u1, u2, m1, m2 = c(u_right_1, np.float32), c(u_right_2, np.float32), c(has_mp_1, np.uint8), c(has_mp_2, np.uint8)
@@ -309,7 +310,7 @@ def search_for_triangulation(desc_1, kps_1, u_right_1, has_mp_1, fv_1, desc_2, k
     p = lambda a: _ptr(a) if a is not None else None  # noqa: E731
     nm = lib().orc_search_for_triangulation(p(d1), p(k1), p(u1), p(m1), d1.shape[0], p(n1), p(s1), p(f1), len(n1), p(d2), p(k2), p(u2), p(m2), d2.shape[0],
                                             p(n2), p(s2), p(f2), len(n2), p(F), p(ep), p(sf), p(ls), th_low, int(only_stereo), int(coarse),
-                                            int(check_orientation), p(out))
+                                            int(check_orientation), p(out), p(rig))
     return out[:d1.shape[0]], nm
 
 

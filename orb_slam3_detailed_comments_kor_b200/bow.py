@@ -100,8 +100,14 @@ def search_by_bow(desc_kf, kps_kf, fv_kf, has_map_point, desc_f, kps_f, fv_f, th
     return match_f[:desc_f.shape[0]], kf_out[:desc_kf.shape[0]], nm.value
 
 
+def make_triangulation_rig(cams, Rs, ts, n_left_1, n_left_2):
+    """orbfe_triangulation_rig: cams = 4 x 8 (camera 1 left / right, camera 2 left / right), Rs = 4 x 3 x 3 and ts = 4 x 3 (ll, lr, rl, rr)."""
+    buf = np.concatenate([np.asarray(cams, np.float32).reshape(32), np.asarray(Rs, np.float32).reshape(36), np.asarray(ts, np.float32).reshape(12)]).astype(np.float32)
+    return np.concatenate([buf.view(np.uint8), np.array([n_left_1, n_left_2], np.int32).view(np.uint8)])
+
+
 def search_for_triangulation(desc_1, kps_1, u_right_1, has_mp_1, fv_1, desc_2, kps_2, u_right_2, has_mp_2, fv_2, f12, epipole, scale_factors,
-                             level_sigma2, th_low=50, only_stereo=False, coarse=False, check_orientation=True, device=0):
+                             level_sigma2, th_low=50, only_stereo=False, coarse=False, check_orientation=True, device=0, rig=None):
     """ORBmatcher::SearchForTriangulation(pKF1, pKF2, F12, ..., bOnlyStereo, bCoarse) (src/ORBmatcher.cc:965-1206) for one pinhole
     keyframe pair on the host.  Returns (vMatches12[n1], nmatches)."""
     c = lambda a, t: None if a is None else np.ascontiguousarray(a, t)  # noqa: E731
@@ -116,5 +122,5 @@ def search_for_triangulation(desc_1, kps_1, u_right_1, has_mp_1, fv_1, desc_2, k
     p = lambda a: ptr(a) if a is not None else None  # noqa: E731
     check(_lib.lib().orbfe_search_for_triangulation(device, p(d1), p(k1), p(u1), p(m1), d1.shape[0], p(n1), p(s1), p(f1), len(n1), p(d2), p(k2), p(u2), p(m2),
                                                     d2.shape[0], p(n2), p(s2), p(f2), len(n2), p(F), p(ep), p(sf), p(ls), len(sf), th_low, int(only_stereo),
-                                                    int(coarse), int(check_orientation), p(out), C.byref(nm)))
+                                                    int(coarse), int(check_orientation), p(out), C.byref(nm), p(rig)))
     return out[:d1.shape[0]], nm.value

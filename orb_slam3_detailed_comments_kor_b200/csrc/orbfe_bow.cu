@@ -23,6 +23,7 @@
 #include <vector>
 
 #include "orbfe_internal.h"
+#include "orbfe_kb8.cuh"
 
 #define BOW_NT 256
 #define BOW_MAXF 4096
@@ -375,6 +376,11 @@ __global__ void __launch_bounds__(SB_NT) k_search_by_bow(int maxF, const int* __
  * src/CameraModels/Pinhole.cpp:135-157: dsqr < 3.84 * mvLevelSigma2[octave2]) or bCoarse; `dist > bestDist` skips, so among equal
  * distances the LAST candidate wins.  This version of the reference never sets vbMatched2, so the features of keyframe 1 are
  * independent of each other: one thread = one feature, no rounds.  Then the rotation histogram as in SearchByBoW. */
+/* RIG: both keyframes come from a two-camera (fisheye) rig (pKF->mpCamera2 != NULL, :990-1003, 1102-1132): rows >= NLeft belong to the right
+ * camera, nothing is "stereo", there is no epipole test, and the constraint is KannalaBrandt8::epipolarConstrain = TriangulateMatches(...) >
+ * 0.0001f with the cameras and the relative pose of the two sides the keypoints sit on. */
+struct TriRig { Kb8Cam cam[4]; float R[4][9], t[4][3]; int nLeft1, nLeft2; };   /* cam: 1 left, 1 right, 2 left, 2 right; poses: ll, lr, rl, rr */
+template <bool RIG>
 __global__ void __launch_bounds__(SB_NT) k_search_for_triangulation(int maxF, const int* __restrict__ pair1, const int* __restrict__ pair2,
                                                                     const uint4* __restrict__ desc, const orbfe_keypoint* __restrict__ kps,
                                                                     const float* __restrict__ uRight, int rowStride, const int* __restrict__ fvNodes,
@@ -383,7 +389,7 @@ __global__ void __launch_bounds__(SB_NT) k_search_for_triangulation(int maxF, co
                                                                     const float* __restrict__ f12All, const float* __restrict__ epAll,
                                                                     const float* __restrict__ scaleFactors, const float* __restrict__ levelSigma2, int thLow,
                                                                     int onlyStereo, int coarse, int checkOri, int* __restrict__ match12,
-                                                                    int* __restrict__ nmatches) {
+                                                                    int* __restrict__ nmatches, const TriRig* __restrict__ rigs) {
     __shared__ int s_rot[32];
     __shared__ int s_total;
     const int tid = threadIdx.x, pr = blockIdx.x;
@@ -412,7 +418,7 @@ __global__ void __launch_bounds__(SB_NT) k_search_for_triangulation(int maxF, co
         for (int j = startsA[e] + (tid & 31); j < startsA[e + 1]; j += 32) {
             const int idx1 = featsA[j];
             if (mpA && mpA[idx1]) continue;                                   /* if(pMP1) continue; */
-            const bool stereo1 = urA && __ldg(urA + idx1) >= 0;
+            const bool stereo1 = !RIG && urA && __ldg(urA + idx1) >= 0;      /* bStereo1 = !pKF1->mpCamera2 && mvuRight[idx1] >= 0 */
             if (onlyStereo && !stereo1) continue;
             const float x1 = __ldg(&kA[idx1].x), y1 = __ldg(&kA[idx1].y);
             /* epipolar line of kp1 in image 2: l = x1' F12 */
@@ -425,18 +431,32 @@ __global__ void __launch_bounds__(SB_NT) k_search_for_triangulation(int maxF, co
             for (int c = fb0; c < fb1; c++) {
                 const int idx2 = featsB[c];
                 if (mpB && mpB[idx2]) continue;                               /* if(vbMatched2[idx2] || pMP2) continue; (vbMatched2 is never set) */
-                const bool stereo2 = urB && __ldg(urB + idx2) >= 0;
+                const bool stereo2 = !RIG && urB && __ldg(urB + idx2) >= 0;
                 if (onlyStereo && !stereo2) continue;
                 const int dist = bow_ham(qa, qb, __ldg(descB + 2 * idx2), __ldg(descB + 2 * idx2 + 1));
                 if (dist > thLow || dist > bestDist) continue;
                 const float x2 = __ldg(&kB[idx2].x), y2 = __ldg(&kB[idx2].y);
                 const int oct2 = __ldg(&kB[idx2].octave);
-                if (!stereo1 && !stereo2) {
+                if (!RIG && !stereo1 && !stereo2) {
                     const float dex = __fsub_rn(epx, x2), dey = __fsub_rn(epy, y2);
                     if (__fadd_rn(__fmul_rn(dex, dex), __fmul_rn(dey, dey)) < __fmul_rn(100.0f, __ldg(scaleFactors + oct2))) continue;
                 }
                 bool ok = coarse != 0;
-                if (!ok && den != 0.0f) {
+                if (RIG) {
+                    if (!ok) {
+                        const TriRig& rg = rigs[pr];
+                        const int r1 = idx1 >= rg.nLeft1 ? 1 : 0, r2 = idx2 >= rg.nLeft2 ? 1 : 0, combo = 2 * r1 + r2;   /* ll, lr, rl, rr */
+                        FisheyeRig fr;
+                        fr.c1 = rg.cam[r1]; fr.c2 = rg.cam[2 + r2];
+#pragma unroll
+                        for (int k = 0; k < 9; k++) fr.R12[k] = rg.R[combo][k];
+#pragma unroll
+                        for (int k = 0; k < 3; k++) fr.t12[k] = rg.t[combo][k];
+                        float x3D[3];
+                        const int oct1 = __ldg(&kA[idx1].octave);
+                        ok = kb8_triangulate_pair(fr, x1, y1, x2, y2, __ldg(levelSigma2 + oct1), __ldg(levelSigma2 + oct2), x3D) > 0.0001f;
+                    }
+                } else if (!ok && den != 0.0f) {
                     const float num = __fadd_rn(__fadd_rn(__fmul_rn(la, x2), __fmul_rn(lb, y2)), lc);
                     const float dsqr = __fdiv_rn(__fmul_rn(num, num), den);
                     ok = (double)dsqr < 3.84 * (double)__ldg(levelSigma2 + oct2);
@@ -737,16 +757,24 @@ int orbfe_search_for_triangulation_device(int device, int npairs, int max_featur
                                           const orbfe_keypoint* d_kps, const float* d_u_right, int row_stride, const int32_t* d_fv_nodes,
                                           const int32_t* d_fv_starts, const int32_t* d_fv_feats, const int32_t* d_fv_count, const uint8_t* d_has_map_point,
                                           const float* d_f12, const float* d_epipole, const float* d_scale_factors, const float* d_level_sigma2, int th_low,
-                                          int only_stereo, int coarse, int check_orientation, int32_t* d_match_12, int32_t* d_nmatches, void* stream) {
+                                          int only_stereo, int coarse, int check_orientation, int32_t* d_match_12, int32_t* d_nmatches, void* stream,
+                                          const orbfe_triangulation_rig* d_rigs) {
     if (npairs < 1 || !d_pair_1 || !d_pair_2 || !d_desc || !d_kps || !d_fv_nodes || !d_fv_starts || !d_fv_feats || !d_fv_count || !d_f12 || !d_epipole ||
         !d_scale_factors || !d_level_sigma2 || !d_match_12 || row_stride < 1) { orbfe_set_error("bad argument"); return ORBFE_E_INVALID; }
     if (max_features < 1 || max_features > BOW_MAXF || row_stride > BOW_MAXF) { orbfe_set_error("at most %d features per frame", BOW_MAXF); return ORBFE_E_CAPACITY; }
     if ((uintptr_t)d_desc & 15) { orbfe_set_error("descriptor array must be 16-byte aligned"); return ORBFE_E_INVALID; }
     ORBFE_CUDA(cudaSetDevice(device));
-    k_search_for_triangulation<<<npairs, SB_NT, 0, (cudaStream_t)stream>>>(max_features, d_pair_1, d_pair_2, (const uint4*)d_desc, d_kps, d_u_right, row_stride,
-                                                                           d_fv_nodes, d_fv_starts, d_fv_feats, d_fv_count, d_has_map_point, d_f12, d_epipole,
-                                                                           d_scale_factors, d_level_sigma2, th_low, only_stereo ? 1 : 0, coarse ? 1 : 0,
-                                                                           check_orientation ? 1 : 0, d_match_12, d_nmatches);
+    static_assert(sizeof(TriRig) == sizeof(orbfe_triangulation_rig), "rig layout");
+    if (d_rigs)
+        k_search_for_triangulation<true><<<npairs, SB_NT, 0, (cudaStream_t)stream>>>(max_features, d_pair_1, d_pair_2, (const uint4*)d_desc, d_kps, d_u_right, row_stride,
+                                                                                     d_fv_nodes, d_fv_starts, d_fv_feats, d_fv_count, d_has_map_point, d_f12, d_epipole,
+                                                                                     d_scale_factors, d_level_sigma2, th_low, only_stereo ? 1 : 0, coarse ? 1 : 0,
+                                                                                     check_orientation ? 1 : 0, d_match_12, d_nmatches, (const TriRig*)d_rigs);
+    else
+        k_search_for_triangulation<false><<<npairs, SB_NT, 0, (cudaStream_t)stream>>>(max_features, d_pair_1, d_pair_2, (const uint4*)d_desc, d_kps, d_u_right, row_stride,
+                                                                                      d_fv_nodes, d_fv_starts, d_fv_feats, d_fv_count, d_has_map_point, d_f12, d_epipole,
+                                                                                      d_scale_factors, d_level_sigma2, th_low, only_stereo ? 1 : 0, coarse ? 1 : 0,
+                                                                                      check_orientation ? 1 : 0, d_match_12, d_nmatches, nullptr);
     ORBFE_CUDA(cudaGetLastError());
     return ORBFE_OK;
 }
@@ -756,7 +784,7 @@ int orbfe_search_for_triangulation(int device, const uint8_t* desc_1, const orbf
                                    const orbfe_keypoint* kps_2, const float* u_right_2, const uint8_t* has_map_point_2, int n_2, const int32_t* fv_nodes_2,
                                    const int32_t* fv_starts_2, const int32_t* fv_feats_2, int nfv_2, const float* f12, const float* epipole,
                                    const float* scale_factors, const float* level_sigma2, int nlevels, int th_low, int only_stereo, int coarse,
-                                   int check_orientation, int32_t* match_12, int* nmatches) {
+                                   int check_orientation, int32_t* match_12, int* nmatches, const orbfe_triangulation_rig* rig) {
     if (n_1 < 0 || n_2 < 0 || nfv_1 < 0 || nfv_2 < 0 || !match_12 || !f12 || !epipole || !scale_factors || !level_sigma2 || nlevels < 1 || nlevels > 16 ||
         (n_1 && (!desc_1 || !kps_1)) || (n_2 && (!desc_2 || !kps_2)) || (nfv_1 && (!fv_nodes_1 || !fv_starts_1 || !fv_feats_1)) ||
         (nfv_2 && (!fv_nodes_2 || !fv_starts_2 || !fv_feats_2))) { orbfe_set_error("bad argument"); return ORBFE_E_INVALID; }
@@ -790,7 +818,7 @@ int orbfe_search_for_triangulation(int device, const uint8_t* desc_1, const orbf
     auto take = [&](size_t bytes) { const size_t o = off; off += (bytes + 255) & ~(size_t)255; return o; };
     const size_t oDesc = take(hDesc.size()), oKps = take(hKps.size() * sizeof(orbfe_keypoint)), oUr = take(hUr.size() * 4), oMp = take(hMp.size());
     const size_t oNodes = take(hNodes.size() * 4), oStarts = take(hStarts.size() * 4), oFeats = take(hFeats.size() * 4), oPar = take(hPar.size() * 4);
-    const size_t oMisc = take(16), oMatch = take((size_t)S * 4), oNm = take(4);
+    const size_t oMisc = take(16), oMatch = take((size_t)S * 4), oNm = take(4), oRig = take(sizeof(orbfe_triangulation_rig));
     uint8_t* d = nullptr;
     ORBFE_CUDA(cudaMalloc((void**)&d, off));
     cudaError_t e = cudaMemcpy(d + oDesc, hDesc.data(), hDesc.size(), cudaMemcpyHostToDevice);
@@ -798,6 +826,7 @@ int orbfe_search_for_triangulation(int device, const uint8_t* desc_1, const orbf
     ST_UP(oKps, hKps.data(), hKps.size() * sizeof(orbfe_keypoint)); ST_UP(oUr, hUr.data(), hUr.size() * 4); ST_UP(oMp, hMp.data(), hMp.size());
     ST_UP(oNodes, hNodes.data(), hNodes.size() * 4); ST_UP(oStarts, hStarts.data(), hStarts.size() * 4); ST_UP(oFeats, hFeats.data(), hFeats.size() * 4);
     ST_UP(oPar, hPar.data(), hPar.size() * 4); ST_UP(oMisc, hMisc.data(), 16);
+    if (rig) ST_UP(oRig, rig, sizeof(orbfe_triangulation_rig));
 #undef ST_UP
     int rc = ORBFE_OK;
     const float* dp = (const float*)(d + oPar);
@@ -805,7 +834,7 @@ int orbfe_search_for_triangulation(int device, const uint8_t* desc_1, const orbf
         rc = orbfe_search_for_triangulation_device(device, 1, S, (const int32_t*)(d + oMisc) + 2, (const int32_t*)(d + oMisc) + 3, d + oDesc, (const orbfe_keypoint*)(d + oKps),
                                                    (const float*)(d + oUr), S, (const int32_t*)(d + oNodes), (const int32_t*)(d + oStarts), (const int32_t*)(d + oFeats),
                                                    (const int32_t*)(d + oMisc), d + oMp, dp, dp + 9, dp + 11, dp + 27, th_low, only_stereo, coarse, check_orientation,
-                                                   (int32_t*)(d + oMatch), (int32_t*)(d + oNm), nullptr);
+                                                   (int32_t*)(d + oMatch), (int32_t*)(d + oNm), nullptr, rig ? (const orbfe_triangulation_rig*)(d + oRig) : nullptr);
     if (rc == ORBFE_OK && e == cudaSuccess) e = cudaStreamSynchronize(nullptr);   /* the launch above went to the default stream */
     if (rc == ORBFE_OK && e == cudaSuccess && n_1) e = cudaMemcpy(match_12, d + oMatch, (size_t)n_1 * 4, cudaMemcpyDeviceToHost);
     if (rc == ORBFE_OK && e == cudaSuccess && nmatches) e = cudaMemcpy(nmatches, d + oNm, 4, cudaMemcpyDeviceToHost);
