@@ -385,13 +385,22 @@ def run_workload(args, wl, rank, world, local_rank, barrier, max_over_ranks):
         else:
             M.compute_stereo_matches(exL, exR, SUB, MBF, 0.0, FX, stream)
 
-    def step():
+    def step_serial():   # one stream: what the per-stage event pairs see
         for s0 in range(0, P, SUB):
             exL.extract_batch_device(dL.data_ptr() + s0 * fb, SUB, LAP, st)
             exR.extract_batch_device(dR.data_ptr() + s0 * fb, SUB, LAP, st)
             match(st)
 
+    def step():          # the product calls: left / right side by side on the two objects' streams
+        for s0 in range(0, P, SUB):
+            if fisheye:
+                M.extract_pair_batch_device(exL, exR, dL.data_ptr() + s0 * fb, dR.data_ptr() + s0 * fb, SUB, LAP, st)
+                match(st)
+            else:
+                M.stereo_frames_batch_device(exL, exR, dL.data_ptr() + s0 * fb, dR.data_ptr() + s0 * fb, SUB, MBF, 0.0, FX, LAP, st)
+
     for _ in range(args.warmup):
+        step_serial()
         step()
     barrier()
     sampler = ClockSampler(local_rank)
@@ -408,7 +417,7 @@ def run_workload(args, wl, rank, world, local_rank, barrier, max_over_ranks):
     for ex in (exL, exR):
         _lib.check(L.orbfe_set_profiling(ex.handle, 1))
     for _ in range(args.steps):
-        step()
+        step_serial()
     torch.cuda.synchronize()
     stage_ms = np.zeros(8)
     launches = C.c_int64(0)
@@ -501,7 +510,9 @@ def run_workload(args, wl, rank, world, local_rank, barrier, max_over_ranks):
                 "config": {"workload": WORKLOAD, "pairs_per_gpu_per_step": P, "frames_per_step": 2 * P * world, "sub_batch_pairs": SUB,
                            "distinct_pairs": min(P, 64), "lapping": list(LAP), "matching": wl["match"],
                            "l2": "inputs_larger_than_L2 (%d MB of images per step per GPU)" % (2 * P * W * H >> 20),
-                           "mean_keypoints_per_frame": nkp, "parallelism": "frames sharded by rank, no collective"},
+                           "mean_keypoints_per_frame": nkp, "parallelism": "frames sharded by rank, no collective",
+                           "schedule": "left and right extraction on the two objects' streams (the reference's two ExtractORB threads), blur beside "
+                                       "quadtree + assemble, matching behind both; timed by events on the caller's stream"},
                 "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
                 "gpu_launches": nsub * (2 * (PARAMS[2] + 8) + (2 if fisheye else 3)) * args.steps}
         print(json.dumps(line), flush=True)
@@ -573,11 +584,24 @@ def main():
     assert st != 0
     L = _lib.lib()
 
-    def step():
+    def step_serial():   # every kernel of both images on the one stream: what the per-stage event pairs and the ncu launch list see
         exL.extract_batch_device(dL.data_ptr(), P, (0, 0), st)
         exR.extract_batch_device(dR.data_ptr(), P, (0, 0), st)
         M.compute_stereo_matches(exL, exR, P, MBF, 0.0, FX, st)
 
+    def step():          # the product call for a batch of device-resident pairs: left / right side by side like the reference's two threads
+        M.stereo_frames_batch_device(exL, exR, dL.data_ptr(), dR.data_ptr(), P, MBF, 0.0, FX, (0, 0), st)
+
+    for _ in range(args.warmup):
+        step_serial()
+    torch.cuda.synchronize()
+    es0, es1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    es0.record()
+    for _ in range(args.steps):
+        step_serial()
+    es1.record()
+    torch.cuda.synchronize()
+    ms_serial = es0.elapsed_time(es1) / args.steps
     for _ in range(args.warmup):
         step()
     barrier()
@@ -597,7 +621,7 @@ def main():
     for ex in (exL, exR):
         _lib.check(L.orbfe_set_profiling(ex.handle, 1))
     for _ in range(args.steps):
-        step()
+        step_serial()
     torch.cuda.synchronize()
     stage_ms = np.zeros(8)
     launches = C.c_int64(0)
@@ -962,7 +986,10 @@ def main():
                 "vs_baseline": None, "dtype": "u8", "data": "synthetic",
                 "config": {"workload": WORKLOAD, "pairs_per_gpu_per_step": P, "frames_per_step": 2 * P * world,
                            "l2": "inputs_larger_than_L2 (%d MB of images per step per GPU)" % (2 * P * W * H >> 20),
-                           "mean_keypoints_per_frame": nkp, "parallelism": "frames sharded by rank, no collective"},
+                           "mean_keypoints_per_frame": nkp, "parallelism": "frames sharded by rank, no collective",
+                           "schedule": "orbfe_stereo_frames_batch_device: left and right extraction on the two objects' streams (the reference's two "
+                                       "ExtractORB threads), blur beside quadtree + assemble, ComputeStereoMatches behind both; timed by events on the caller's stream",
+                           "serial_ms_per_step": ms_serial},
                 "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
                 "single_frame_latency_ms": single_ms, "shim_single_frame_latency_ms": shim_ms, "rectify": rectify, "projection": projection, "bow": bow,
                 "gpu_launches": (2 * (PARAMS[2] + 8) + 3) * args.steps,

@@ -95,6 +95,17 @@ int orbfe_extract(orbfe_extractor* ex, const uint8_t* image, int rows, int cols,
  * This is the call the roofline numbers are quoted on (frames are independent: SURVEY.md §8e). */
 int orbfe_extract_batch_device(orbfe_extractor* ex, const uint8_t* d_images, int nframes, int lap0, int lap1,
                                void* stream);
+/* Frame's stereo constructor (src/Frame.cc:104-170) for a batch of pairs that already sit in device memory: the reference runs
+ * the two ExtractORB calls on two threads (:119-122) and ComputeStereoMatches when both are back (:136); here the left images go
+ * through exL on its own stream, the right ones through exR on its own stream, the matching follows on the left stream.  `stream`
+ * (may be NULL) is the caller's: the work starts after what that stream holds now and is complete, for that stream, after the
+ * call (fork / join by events, the host is never blocked).  Results as after orbfe_extract_batch_device + orbfe_stereo_match_batch_device. */
+int orbfe_stereo_frames_batch_device(orbfe_extractor* exL, orbfe_extractor* exR, const uint8_t* d_left, const uint8_t* d_right, int nframes, int lap0,
+                                     int lap1, float mbf, float min_d, float max_d, void* stream);
+/* The same without the matcher: the two extractions of Frame's fisheye-rig constructor (src/Frame.cc:1051-1054), side by side; the
+ * caller continues on `stream` with orbfe_fisheye_match_batch_device / orbfe_fisheye_triangulate_batch_device (or any other consumer). */
+int orbfe_extract_pair_batch_device(orbfe_extractor* exL, orbfe_extractor* exR, const uint8_t* d_left, const uint8_t* d_right, int nframes, int lap0,
+                                    int lap1, void* stream);
 /* Same, from host memory (pinned or pageable): host->device copy, extraction, device->host copy of the results.
  * kps: nframes*cap entries, desc: nframes*cap*32 bytes, n / mono_index: nframes ints.  Synchronous. */
 int orbfe_extract_batch_host(orbfe_extractor* ex, const uint8_t* h_images, int nframes, int lap0, int lap1,

@@ -65,6 +65,8 @@ SIGNATURES = {
     "orbfe_blurred_level": (i32, [vp, i32, i32, vp]),
     "orbfe_fast_candidates": (i32, [vp, i32, i32, vp, i32, C.POINTER(i32)]),
     "orbfe_stereo_match_batch_device": (i32, [vp, vp, i32, f32, f32, f32, vp]),
+    "orbfe_stereo_frames_batch_device": (i32, [vp, vp, vp, vp, i32, i32, i32, f32, f32, f32, vp]),
+    "orbfe_extract_pair_batch_device": (i32, [vp, vp, vp, vp, i32, i32, i32, vp]),
     "orbfe_stereo_result": (i32, [vp, i32, vp, vp, i32, C.POINTER(i32)]),
     "orbfe_stereo_result_batch": (i32, [vp, i32, vp, vp, i32]),
     "orbfe_set_profiling": (i32, [vp, i32]),

@@ -1405,6 +1405,26 @@ int orbfe_configure_kernels(int quadSmem, int fastSmem) {
     ORBFE_CUDA(cudaGetDevice(&dev));
     if (dev < 0 || dev >= ORBFE_MAX_DEVICES) { orbfe_set_error("device ordinal %d out of range", dev); return ORBFE_E_INVALID; }
     std::lock_guard<std::mutex> lock(mu);
+    static bool carved[ORBFE_MAX_DEVICES];
+    if (!carved[dev]) {
+        /* Shared-memory carve-out per kernel, in percent of the SM's 228 KB.  Left to the driver the split is chosen from what ran
+         * before, and a step measured 3.34 or 3.49 ms depending on which call an object saw first; fixed, every kernel gets the
+         * split it was fastest with in a sweep over 25 / 50 / 75 / 100 (the table is in DESIGN.md section 4) and kernels of the two
+         * images that meet on an SM agree on it. */
+        ORBFE_CUDA(cudaFuncSetAttribute(k_pyramid_copy0, cudaFuncAttributePreferredSharedMemoryCarveout, 25));
+        ORBFE_CUDA(cudaFuncSetAttribute(k_pyramid_level, cudaFuncAttributePreferredSharedMemoryCarveout, 25));
+        ORBFE_CUDA(cudaFuncSetAttribute(k_pyramid_fringe, cudaFuncAttributePreferredSharedMemoryCarveout, 25));
+        ORBFE_CUDA(cudaFuncSetAttribute(k_fast_stream, cudaFuncAttributePreferredSharedMemoryCarveout, 50));
+        ORBFE_CUDA(cudaFuncSetAttribute(k_fast_nms, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+        ORBFE_CUDA(cudaFuncSetAttribute(k_fast_cells_list, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+        ORBFE_CUDA(cudaFuncSetAttribute(k_blur7_tma, cudaFuncAttributePreferredSharedMemoryCarveout, 75));
+        ORBFE_CUDA(cudaFuncSetAttribute(k_blur7, cudaFuncAttributePreferredSharedMemoryCarveout, 75));
+        ORBFE_CUDA(cudaFuncSetAttribute(k_quadtree<false>, cudaFuncAttributePreferredSharedMemoryCarveout, 75));
+        ORBFE_CUDA(cudaFuncSetAttribute(k_quadtree<true>, cudaFuncAttributePreferredSharedMemoryCarveout, 75));
+        ORBFE_CUDA(cudaFuncSetAttribute(k_assemble, cudaFuncAttributePreferredSharedMemoryCarveout, 75));
+        ORBFE_CUDA(cudaFuncSetAttribute(k_orient_describe, cudaFuncAttributePreferredSharedMemoryCarveout, 50));
+        carved[dev] = true;
+    }
     if (quadSmem > quadMax[dev]) {
         ORBFE_CUDA(cudaFuncSetAttribute(k_quadtree<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, quadSmem));
         quadMax[dev] = quadSmem;
@@ -1472,14 +1492,25 @@ int orbfe_launch_extract(orbfe_extractor* ex, const uint8_t* d_images, int nfram
     k_fast_nms<<<dim3((d.nCells + FN_WARPS - 1) / FN_WARPS, nframes), FN_WARPS * 32, 0, st>>>(d, xb);
     k_fast_cells_list<<<148 * 8, FAST_NT, ex->fastSmem, st>>>(d, xb);
     STAGE_MARK();
-    if (ex->blurLdg) k_blur7<<<dim3(d.blurTile0[d.nlevels], nframes), 256, 0, st>>>(d, xb);
-    else k_blur7_tma<<<dim3(d.blurTile0[d.nlevels], nframes), 256, 0, st>>>(d, xb, ex->blurMaps, frame0);
+    /* The blur needs only the pyramid, quadtree + assemble only the corners: they run side by side (the quadtree is a few long
+     * latency-bound CTAs per frame, the blur fills the issue slots they leave empty) and meet again in front of k_orient_describe.
+     * With stage profiling on everything stays on `st` so that the per-stage event pairs keep their meaning. */
+    const bool fork = ex->forkBlur && !prof;
+    const cudaStream_t bs = fork ? ex->side : st;
+    if (fork) {
+        ORBFE_CUDA(cudaEventRecord(ex->evFork, st));
+        ORBFE_CUDA(cudaStreamWaitEvent(bs, ex->evFork, 0));
+    }
+    if (ex->blurLdg) k_blur7<<<dim3(d.blurTile0[d.nlevels], nframes), 256, 0, bs>>>(d, xb);
+    else k_blur7_tma<<<dim3(d.blurTile0[d.nlevels], nframes), 256, 0, bs>>>(d, xb, ex->blurMaps, frame0);
+    if (fork) ORBFE_CUDA(cudaEventRecord(ex->evJoin, bs));
     STAGE_MARK();
     if (d.qtScratchBytes) k_quadtree<true><<<dim3(d.nlevels, nframes), QT_NT, 0, st>>>(d, xb);
     else k_quadtree<false><<<dim3(d.nlevels, nframes), QT_NT, ex->quadSmem, st>>>(d, xb);
     STAGE_MARK();
     k_assemble<<<nframes, AS_NT, 0, st>>>(d, xb, lap0, lap1);
     STAGE_MARK();
+    if (fork) ORBFE_CUDA(cudaStreamWaitEvent(st, ex->evJoin, 0));
     k_orient_describe<<<dim3((d.kpCap + OD_NT / 32 - 1) / (OD_NT / 32), nframes), OD_NT, 0, st>>>(d, xb);
     STAGE_MARK();
 #undef STAGE_MARK

@@ -122,6 +122,9 @@ void orbfe_extractor_destroy(orbfe_extractor* ex) {
     for (cudaEvent_t ev : ex->evOut) if (ev) cudaEventDestroy(ev);
     for (cudaEvent_t ev : ex->evBatch) if (ev) cudaEventDestroy(ev);
     if (ex->evLast) cudaEventDestroy(ex->evLast);
+    if (ex->evFork) cudaEventDestroy(ex->evFork);
+    if (ex->evJoin) cudaEventDestroy(ex->evJoin);
+    if (ex->side) cudaStreamDestroy(ex->side);
     if (ex->copyIn) cudaStreamDestroy(ex->copyIn);
     if (ex->copyOut) cudaStreamDestroy(ex->copyOut);
     if (ex->stream) cudaStreamDestroy(ex->stream);
@@ -153,7 +156,7 @@ int orbfe_extractor_create(const orbfe_params* p, int device, int width, int hei
     ex->maxBatch = max_batch;
     ex->lastBatch = 0;
     ex->params = *p;
-    ex->stream = nullptr; ex->copyIn = nullptr; ex->copyOut = nullptr;
+    ex->stream = nullptr; ex->copyIn = nullptr; ex->copyOut = nullptr; ex->side = nullptr; ex->evFork = nullptr; ex->evJoin = nullptr; ex->forkBlur = 1;
     ex->hKps = nullptr; ex->hDesc = nullptr; ex->hCount = nullptr; ex->hMono = nullptr;
     ex->profiling = 0; ex->stagePending = 0; ex->stereoPending = 0; ex->launches = 0; ex->batchFrames = 0; ex->bordersValid = 0;
     ex->graphExec = nullptr; ex->graphLap0 = ex->graphLap1 = 0; ex->graphLaunches = 0; ex->singleGraph = 1;
@@ -354,6 +357,10 @@ int orbfe_extractor_create(const orbfe_params* p, int device, int width, int hei
     TRYC(cudaStreamCreateWithFlags(&ex->stream, cudaStreamNonBlocking));
     TRYC(cudaStreamCreateWithFlags(&ex->copyIn, cudaStreamNonBlocking));
     TRYC(cudaStreamCreateWithFlags(&ex->copyOut, cudaStreamNonBlocking));
+    TRYC(cudaStreamCreateWithFlags(&ex->side, cudaStreamNonBlocking));
+    TRYC(cudaEventCreateWithFlags(&ex->evFork, cudaEventDisableTiming));
+    TRYC(cudaEventCreateWithFlags(&ex->evJoin, cudaEventDisableTiming));
+    if (const char* e = getenv("ORBFE_NO_FORK")) ex->forkBlur = atoi(e) ? 0 : 1;
     ex->hostChunk = ORBFE_HOST_CHUNK;
     if (const char* e = getenv("ORBFE_HOST_CHUNK")) { const int v = atoi(e); if (v >= 1) ex->hostChunk = v; }
     ex->evIn.assign((max_batch + ex->hostChunk - 1) / ex->hostChunk, nullptr);
@@ -503,6 +510,63 @@ int orbfe_extract_batch_device(orbfe_extractor* ex, const uint8_t* d_images, int
     cudaStream_t st = stream ? (cudaStream_t)stream : ex->stream;
     const int rc = orbfe_launch_extract(ex, d_images, nframes, lap0, lap1, st, 0);
     return rc ? rc : orbfe_mark_last(ex, st);
+}
+
+/* The stereo Frame constructors (src/Frame.cc:104-170 rectified stereo, :1023-1101 fisheye rig) for a batch of pairs already on
+ * the device: the reference extracts the two images on two threads (:119-122, :1051-1054) and matches when both are back; here the
+ * left images go through exL on its stream, the right ones through exR on its stream, and (match != 0) ComputeStereoMatches
+ * follows on the left stream once the right one is done.  `user` (may be null) is the caller's stream: everything enqueued here
+ * starts after what it holds now and is finished, for that stream, when the call returns (fork / join by events; nothing blocks
+ * the host). */
+static int pair_batch_device(orbfe_extractor* exL, orbfe_extractor* exR, const uint8_t* d_left, const uint8_t* d_right, int nframes, int lap0, int lap1,
+                             int match, float mbf, float min_d, float max_d, cudaStream_t user) {
+    if (!exL || !exR || !d_left || !d_right) { orbfe_set_error("null argument"); return ORBFE_E_INVALID; }
+    if (exL == exR || exL->device != exR->device || exL->d.W != exR->d.W || exL->d.H != exR->d.H || exL->d.kpCap != exR->d.kpCap || exL->d.nlevels != exR->d.nlevels) {
+        orbfe_set_error("left/right extractors must be two objects of the same geometry on one device");
+        return ORBFE_E_INVALID;
+    }
+    if (nframes < 1 || nframes > exL->maxBatch || nframes > exR->maxBatch) {
+        orbfe_set_error("nframes %d outside [1, max_batch=%d]", nframes, exL->maxBatch < exR->maxBatch ? exL->maxBatch : exR->maxBatch);
+        return ORBFE_E_CAPACITY;
+    }
+    ORBFE_CUDA(cudaSetDevice(exL->device));
+    cudaStream_t sl = exL->stream, sr = exR->stream;
+    if (user) {
+        ORBFE_CUDA(cudaEventRecord(exL->evIn[0], user));
+        ORBFE_CUDA(cudaStreamWaitEvent(sl, exL->evIn[0], 0));
+        ORBFE_CUDA(cudaStreamWaitEvent(sr, exL->evIn[0], 0));
+    }
+    exL->lastBatch = exR->lastBatch = nframes;
+    int rc = orbfe_launch_extract(exL, d_left, nframes, lap0, lap1, sl, 0);
+    if (rc) return rc;
+    rc = orbfe_launch_extract(exR, d_right, nframes, lap0, lap1, sr, 0);
+    if (rc) return rc;
+    ORBFE_CUDA(cudaEventRecord(exR->evDone[0], sr));
+    ORBFE_CUDA(cudaStreamWaitEvent(sl, exR->evDone[0], 0));
+    if (match) {
+        rc = orbfe_launch_stereo(exL, exR, nframes, 0, mbf, min_d, max_d, sl);
+        if (rc) return rc;
+    }
+    /* the right object's next batch must not overwrite what a matcher on the left stream (or on the caller's) still reads */
+    ORBFE_CUDA(cudaEventRecord(exL->evDone[0], sl));
+    ORBFE_CUDA(cudaStreamWaitEvent(sr, exL->evDone[0], 0));
+    if (user) {
+        ORBFE_CUDA(cudaStreamWaitEvent(user, exL->evDone[0], 0));
+        rc = orbfe_mark_last(exL, user);
+        return rc ? rc : orbfe_mark_last(exR, user);
+    }
+    rc = orbfe_mark_last(exL, sl);
+    return rc ? rc : orbfe_mark_last(exR, sl);
+}
+
+int orbfe_stereo_frames_batch_device(orbfe_extractor* exL, orbfe_extractor* exR, const uint8_t* d_left, const uint8_t* d_right, int nframes, int lap0, int lap1,
+                                     float mbf, float min_d, float max_d, void* stream) {
+    return pair_batch_device(exL, exR, d_left, d_right, nframes, lap0, lap1, 1, mbf, min_d, max_d, (cudaStream_t)stream);
+}
+
+int orbfe_extract_pair_batch_device(orbfe_extractor* exL, orbfe_extractor* exR, const uint8_t* d_left, const uint8_t* d_right, int nframes, int lap0, int lap1,
+                                    void* stream) {
+    return pair_batch_device(exL, exR, d_left, d_right, nframes, lap0, lap1, 0, 0.f, 0.f, 0.f, (cudaStream_t)stream);
 }
 
 int orbfe_batch_counts(orbfe_extractor* ex, int nframes, int32_t* n, int32_t* mono) {

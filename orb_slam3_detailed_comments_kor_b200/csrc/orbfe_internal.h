@@ -126,6 +126,9 @@ struct orbfe_extractor {
     uint8_t* inputStage;  /* device copy of host images */
     cudaStream_t stream;
     cudaStream_t copyIn, copyOut;          /* host-batch pipeline: uploads and downloads overlap the kernels */
+    cudaStream_t side;                     /* the blur runs here, beside quadtree + assemble (they only meet again in k_orient_describe) */
+    cudaEvent_t evFork, evJoin;
+    int forkBlur;                          /* 0 with ORBFE_NO_FORK=1 */
     std::vector<cudaEvent_t> evIn, evDone; /* one pair per chunk of hostChunk frames */
     std::vector<cudaEvent_t> evOut;        /* per chunk: the download of its results has finished (next batch may rewrite them) */
     std::vector<char> evOutValid;

@@ -96,6 +96,19 @@ def compute_stereo_matches(exL, exR, nframes, mbf, minD, maxD, stream=None):
                                                      C.c_void_p(stream) if stream else None))
 
 
+def stereo_frames_batch_device(exL, exR, d_left_ptr, d_right_ptr, nframes, mbf, minD, maxD, vLappingArea=(0, 0), stream=None):
+    """Frame's stereo constructor for a batch of device-resident pairs (src/Frame.cc:104-170): left and right extraction side by
+    side on the two objects' streams, ComputeStereoMatches behind them; ordered after and before the caller's `stream`."""
+    check(_lib.lib().orbfe_stereo_frames_batch_device(exL.handle, exR.handle, C.c_void_p(d_left_ptr), C.c_void_p(d_right_ptr), nframes,
+                                                      int(vLappingArea[0]), int(vLappingArea[1]), mbf, minD, maxD, C.c_void_p(stream) if stream else None))
+
+
+def extract_pair_batch_device(exL, exR, d_left_ptr, d_right_ptr, nframes, vLappingArea=(0, 0), stream=None):
+    """The two ExtractORB threads of Frame's rig constructor (src/Frame.cc:1051-1054) for a batch of device-resident pairs."""
+    check(_lib.lib().orbfe_extract_pair_batch_device(exL.handle, exR.handle, C.c_void_p(d_left_ptr), C.c_void_p(d_right_ptr), nframes,
+                                                     int(vLappingArea[0]), int(vLappingArea[1]), C.c_void_p(stream) if stream else None))
+
+
 def stereo_frames_batch_host(exL, exR, left, right, mbf, minD, maxD, vLappingArea=(0, 0), out=None):
     """Frame's stereo constructor for a batch of pairs (src/Frame.cc:104-178): both extractions and ComputeStereoMatches,
     pipelined over chunks inside one call.  left / right: [n, H, W] u8 host arrays.  Returns

@@ -406,6 +406,64 @@ def test_stereo_frames_submit_wait_keeps_two_batches_in_flight():
     exL.close(); exR.close()
 
 
+def test_stereo_frames_batch_device_left_right_side_by_side():
+    """orbfe_stereo_frames_batch_device / orbfe_extract_pair_batch_device (left and right on their own streams, the blur beside the
+    quadtree) against the oracle for the first pairs and against the one-stream calls for all; repeated, on the caller's stream and
+    without one, with a consumer enqueued right behind on the caller's stream."""
+    import torch
+    W, H, params, nb = 320, 240, (500, 1.2, 8, 20, 7), 24
+    pairs = [synth.stereo_pair(4100 + i, W, H) for i in range(nb)]
+    dLs = torch.from_numpy(np.stack([p[0] for p in pairs])).cuda()
+    dRs = torch.from_numpy(np.stack([p[1] for p in pairs])).cuda()
+    exL = ORBextractor(*params, width=W, height=H, max_batch=nb)
+    exR = ORBextractor(*params, width=W, height=H, max_batch=nb)
+    st = torch.cuda.Stream()
+    exL.extract_batch_device(dLs.data_ptr(), nb, (0, 0), st.cuda_stream)
+    exR.extract_batch_device(dRs.data_ptr(), nb, (0, 0), st.cuda_stream)
+    M.compute_stereo_matches(exL, exR, nb, 40.0, 0.0, 300.0, st.cuda_stream)
+    torch.cuda.synchronize()
+
+    def snapshot():
+        out = []
+        for f in range(nb):
+            ml, kl, dl = exL.batch_result(f)
+            mr, kr, dr = exR.batch_result(f)
+            u, d = M.stereo_result(exL, f)
+            out.append((ml, kl.copy(), dl.copy(), mr, kr.copy(), dr.copy(), u.copy(), d.copy()))
+        return out
+    want = snapshot()
+    oL, oR = O.OracleExtractor(*params), O.OracleExtractor(*params)
+    for f in range(3):
+        _, okl, odl = oL(pairs[f][0], (0, 0))
+        _, okr, odr = oR(pairs[f][1], (0, 0))
+        assert_same_keypoints(want[f][1], okl)
+        assert np.array_equal(want[f][2], odl)
+        _, ou, od = O.stereo_match(oL, oR, okl, odl, okr, odr, 40.0, 0.0, 300.0)
+        assert np.array_equal(want[f][6], ou) and np.array_equal(want[f][7], od)
+    for rep, stream in enumerate([st, None, st]):
+        with torch.cuda.stream(st):
+            dLs2, dRs2 = dLs.clone(), dRs.clone()                       # produced on the caller's stream right before the call
+        M.stereo_frames_batch_device(exL, exR, dLs2.data_ptr(), dRs2.data_ptr(), nb, 40.0, 0.0, 300.0, (0, 0), stream.cuda_stream if stream else None)
+        if stream is None:
+            torch.cuda.synchronize()                                        # no caller stream: the getters wait for the objects themselves
+        got = snapshot()
+        for f in range(nb):
+            for a, b in zip(got[f], want[f]):
+                assert np.array_equal(a, b), "rep %d frame %d" % (rep, f)
+    # the rig variant: both extractions, then a consumer (the stereo matcher as a separate call) on the caller's stream
+    M.extract_pair_batch_device(exL, exR, dLs.data_ptr(), dRs.data_ptr(), nb, (0, 0), st.cuda_stream)
+    M.compute_stereo_matches(exL, exR, nb, 40.0, 0.0, 300.0, st.cuda_stream)
+    got = snapshot()
+    for f in range(nb):
+        for a, b in zip(got[f], want[f]):
+            assert np.array_equal(a, b), "pair call, frame %d" % f
+    with pytest.raises(OrbfeError):
+        M.stereo_frames_batch_device(exL, exL, dLs.data_ptr(), dRs.data_ptr(), nb, 40.0, 0.0, 300.0)
+    with pytest.raises(OrbfeError):
+        M.stereo_frames_batch_device(exL, exR, dLs.data_ptr(), dRs.data_ptr(), nb + 1, 40.0, 0.0, 300.0)
+    exL.close(); exR.close()
+
+
 def test_kitti_full_size_batch_properties():
     """BASELINE config 4 at full size: 4096 KITTI-shaped images (2048 stereo pairs, 1241x376, 2000 features) in one device
     batch per camera.  The batch is 16 distinct pairs repeated in a scrambled order: every frame must give exactly what its
