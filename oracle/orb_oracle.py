@@ -76,6 +76,8 @@ def lib():
     L.orc_distinctive_descriptors.argtypes = [vp, vp, C.c_int, vp, vp]
     L.orc_search_by_projection.argtypes = [vp, vp, C.c_int, C.c_int, vp, vp, vp, vp, vp, vp, C.c_int, C.c_int, C.c_float, C.c_int, vp, vp]
     L.orc_search_by_projection.restype = C.c_int
+    L.orc_search_for_initialization.argtypes = [vp, vp, C.c_int, vp, vp, C.c_int, vp, vp, C.c_int, C.c_float, C.c_int, C.c_int, vp]
+    L.orc_search_for_initialization.restype = C.c_int
     L.orc_clahe_u8.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_double, C.c_int, C.c_int, vp, C.c_int, vp]
     L.orc_clahe_u8.restype = C.c_int
     L.orc_svd4x4_vt.argtypes = [vp, vp, vp]
@@ -348,6 +350,18 @@ def search_by_projection(kps, desc, queries, qdesc, grid, n_left=-1, u_right=Non
                                         _ptr(pt) if pt is not None else None, _ptr(tk), _ptr(grid), _ptr(queries), _ptr(qdesc),
                                         queries.shape[0], th_high, nnratio, int(check_orientation), _ptr(sig) if sig is not None else None, _ptr(out))
     return out, tk, nm
+
+
+def search_for_initialization(kps1, desc1, kps2, desc2, grid, prev_matched, window=100, nnratio=0.9, check_orientation=True, th_low=50):
+    """ORBmatcher::SearchForInitialization (src/ORBmatcher.cc:706-821) on arrays.  Returns (vnMatches12, vbPrevMatched afterwards, nmatches)."""
+    kps1 = np.ascontiguousarray(kps1, KP_DTYPE); kps2 = np.ascontiguousarray(kps2, KP_DTYPE)
+    desc1 = np.ascontiguousarray(desc1, np.uint8); desc2 = np.ascontiguousarray(desc2, np.uint8)
+    grid = np.ascontiguousarray(grid, np.float32)
+    prev = np.array(prev_matched, np.float32).reshape(kps1.shape[0], 2).copy()
+    m12 = np.zeros(kps1.shape[0], np.int32)
+    nm = lib().orc_search_for_initialization(_ptr(kps1), _ptr(desc1), kps1.shape[0], _ptr(kps2), _ptr(desc2), kps2.shape[0], _ptr(grid), _ptr(prev),
+                                             int(window), float(nnratio), int(check_orientation), int(th_low), _ptr(m12))
+    return m12, prev, nm
 
 
 def clahe(img, clip=3.0, tiles=(8, 8), return_lut=False):

@@ -158,4 +158,97 @@ int orc_search_by_projection(const orc_keypoint* kps, const uint8_t* desc, int n
     return nmatches;
 }
 
+/* ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize), /root/reference/src/ORBmatcher.cc:706-821
+ * (the matcher of the monocular initialiser, Tracking.cc:2462), on plain arrays.  kps1 / kps2 are F1.mvKeysUn / F2.mvKeysUn.
+ * The loop is serial: a level-0 keypoint of F1 takes the best level-0 keypoint of F2 inside the window around its previous
+ * match, a keypoint of F2 that is already matched at a distance <= the new one is invisible (:745), a better match displaces
+ * the old one (:764-768); the rotation histogram counts every acceptance, displaced ones included (:783).
+ * prev_matched [n1][2] is updated in place (:816-818); matches12 [n1] receives vnMatches12.  Returns nmatches. */
+int orc_search_for_initialization(const orc_keypoint* kps1, const uint8_t* desc1, int n1, const orc_keypoint* kps2, const uint8_t* desc2, int n2,
+                                  const orc_frame_grid* g, float* prev_matched, int window, float nnratio, int check_orientation, int th_low,
+                                  int32_t* matches12) {
+    Grid* grid = new Grid();
+    for (int i = 0; i < n2; i++) {
+        const int posX = (int)std::round((kps2[i].x - g->min_x) * g->inv_w), posY = (int)std::round((kps2[i].y - g->min_y) * g->inv_h);
+        if (posX < 0 || posX >= GRID_COLS || posY < 0 || posY >= GRID_ROWS) continue;
+        grid->cell[0][posX][posY].push_back(i);
+    }
+    int nmatches = 0;
+    for (int i = 0; i < n1; i++) matches12[i] = -1;
+    std::vector<int> rotHist[HISTO_LENGTH];
+    const float factor = 1.0f / HISTO_LENGTH;
+    std::vector<int> vMatchedDistance(n2, INT32_MAX), vnMatches21(n2, -1);
+    for (int i1 = 0; i1 < n1; i1++) {
+        const int level1 = kps1[i1].octave;
+        if (level1 > 0) continue;
+        std::vector<int> vIndices2;
+        const float x = prev_matched[2 * i1], y = prev_matched[2 * i1 + 1], r = (float)window;
+        do {   /* GetFeaturesInArea(x, y, windowSize, level1, level1) */
+            const int nMinCellX = std::max(0, (int)std::floor((x - g->min_x - r) * g->inv_w));
+            if (nMinCellX >= GRID_COLS) break;
+            const int nMaxCellX = std::min(GRID_COLS - 1, (int)std::ceil((x - g->min_x + r) * g->inv_w));
+            if (nMaxCellX < 0) break;
+            const int nMinCellY = std::max(0, (int)std::floor((y - g->min_y - r) * g->inv_h));
+            if (nMinCellY >= GRID_ROWS) break;
+            const int nMaxCellY = std::min(GRID_ROWS - 1, (int)std::ceil((y - g->min_y + r) * g->inv_h));
+            if (nMaxCellY < 0) break;
+            const bool bCheckLevels = (level1 > 0) || (level1 >= 0);
+            for (int ix = nMinCellX; ix <= nMaxCellX; ix++)
+                for (int iy = nMinCellY; iy <= nMaxCellY; iy++)
+                    for (int idx : grid->cell[0][ix][iy]) {
+                        if (bCheckLevels) {
+                            if (kps2[idx].octave < level1) continue;
+                            if (level1 >= 0 && kps2[idx].octave > level1) continue;
+                        }
+                        const float distx = kps2[idx].x - x, disty = kps2[idx].y - y;
+                        if (std::fabs(distx) < r && std::fabs(disty) < r) vIndices2.push_back(idx);
+                    }
+        } while (false);
+        if (vIndices2.empty()) continue;
+        int bestDist = INT32_MAX, bestDist2 = INT32_MAX, bestIdx2 = -1;
+        for (int i2 : vIndices2) {
+            const int dist = orc_descriptor_distance(desc1 + (size_t)i1 * 32, desc2 + (size_t)i2 * 32);
+            if (vMatchedDistance[i2] <= dist) continue;
+            if (dist < bestDist) { bestDist2 = bestDist; bestDist = dist; bestIdx2 = i2; }
+            else if (dist < bestDist2) bestDist2 = dist;
+        }
+        if (bestDist <= th_low) {
+            if (bestDist < (float)bestDist2 * nnratio) {
+                if (vnMatches21[bestIdx2] >= 0) { matches12[vnMatches21[bestIdx2]] = -1; nmatches--; }
+                matches12[i1] = bestIdx2;
+                vnMatches21[bestIdx2] = i1;
+                vMatchedDistance[bestIdx2] = bestDist;
+                nmatches++;
+                if (check_orientation) {
+                    float rot = kps1[i1].angle - kps2[bestIdx2].angle;
+                    if (rot < 0.0) rot += 360.0f;
+                    int bin = (int)std::round(rot * factor);
+                    if (bin == HISTO_LENGTH) bin = 0;
+                    if (bin >= 0 && bin < HISTO_LENGTH) rotHist[bin].push_back(i1);
+                }
+            }
+        }
+    }
+    if (check_orientation) {
+        int ind1 = -1, ind2 = -1, ind3 = -1, max1 = 0, max2 = 0, max3 = 0;
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            const int s = (int)rotHist[i].size();
+            if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = i; }
+            else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = i; }
+            else if (s > max3) { max3 = s; ind3 = i; }
+        }
+        if (max2 < 0.1f * (float)max1) { ind2 = -1; ind3 = -1; }
+        else if (max3 < 0.1f * (float)max1) { ind3 = -1; }
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            if (i == ind1 || i == ind2 || i == ind3) continue;
+            for (int idx1 : rotHist[i])
+                if (matches12[idx1] >= 0) { matches12[idx1] = -1; nmatches--; }
+        }
+    }
+    for (int i1 = 0; i1 < n1; i1++)
+        if (matches12[i1] >= 0) { prev_matched[2 * i1] = kps2[matches12[i1]].x; prev_matched[2 * i1 + 1] = kps2[matches12[i1]].y; }
+    delete grid;
+    return nmatches;
+}
+
 }  /* extern "C" */

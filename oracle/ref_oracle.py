@@ -50,6 +50,8 @@ def lib(fma=False):
     L.ref_descriptor_distance.argtypes = [vp, vp]
     L.ref_search_by_bow.argtypes = [vp, vp, C.c_int, vp, vp, vp, C.c_int, vp, vp, vp, C.c_int, vp, vp, vp, C.c_int, vp, C.c_int, C.c_float, C.c_int, C.c_int, vp]
     L.ref_distinctive_descriptor.argtypes = [vp, C.c_int, vp]
+    L.ref_search_for_initialization.argtypes = [vp, vp, C.c_int, vp, vp, C.c_int, vp, vp, C.c_int, C.c_float, C.c_int, vp]
+    L.ref_search_for_initialization.restype = C.c_int
     L.ref_search_by_projection.argtypes = [vp, vp, C.c_int, C.c_int, vp, vp, vp, vp, vp, vp, C.c_int, C.c_int] + [vp] * 12 + [C.c_float, C.c_float, vp]
     _libs[fma] = L
     return L
@@ -165,6 +167,18 @@ def search_by_projection(kps, desc, n_left, u_right, l2r, r2l, taken, grid4, sca
     nm = lib().ref_search_by_projection(_ptr(kps), _ptr(desc), n, int(n_left), p(ur), p(a_l2r), p(a_r2l), _ptr(tk), _ptr(g), _ptr(sf), len(sf), len(arrs[0]),
                                         *[_ptr(a) for a in arrs], float(th), float(nnratio), _ptr(owner))
     return owner[:n], nm
+
+
+def search_for_initialization(kps1, desc1, kps2, desc2, grid4, prev_matched, window=100, nnratio=0.9, check_orientation=True):
+    """The reference's own ORBmatcher::SearchForInitialization on arrays.  Returns (vnMatches12, vbPrevMatched afterwards, nmatches)."""
+    kps1, kps2 = np.ascontiguousarray(kps1, KP_DTYPE), np.ascontiguousarray(kps2, KP_DTYPE)
+    desc1, desc2 = np.ascontiguousarray(desc1, np.uint8), np.ascontiguousarray(desc2, np.uint8)
+    g = np.ascontiguousarray(grid4, np.float32)
+    prev = np.array(prev_matched, np.float32).reshape(kps1.shape[0], 2).copy()
+    m12 = np.zeros(max(kps1.shape[0], 1), np.int32)
+    nm = lib().ref_search_for_initialization(_ptr(kps1), _ptr(desc1), kps1.shape[0], _ptr(kps2), _ptr(desc2), kps2.shape[0], _ptr(g), _ptr(prev), int(window),
+                                             float(nnratio), int(check_orientation), _ptr(m12))
+    return m12[:kps1.shape[0]], prev, nm
 
 
 def distinctive_descriptor(desc, bad_kf=None):

@@ -174,6 +174,7 @@ public:
     int SearchByBoW(KeyFrame* pKF, Frame& F, std::vector<MapPoint*>& vpMapPointMatches);
     int SearchByBoW(KeyFrame* pKF1, KeyFrame* pKF2, std::vector<MapPoint*>& vpMatches12);
     int SearchByProjection(Frame& F, const std::vector<MapPoint*>& vpMapPoints, const float th = 3, const bool bFarPoints = false, const float thFarPoints = 50.0f);
+    int SearchForInitialization(Frame& F1, Frame& F2, std::vector<cv::Point2f>& vbPrevMatched, std::vector<int>& vnMatches12, int windowSize = 10);
     float RadiusByViewingCos(const float& viewCos);
     void ComputeThreeMaxima(std::vector<int>* histo, const int L, int& ind1, int& ind2, int& ind3);
     static const int TH_LOW;
@@ -192,6 +193,7 @@ const int ORBmatcher::HISTO_LENGTH = 30;   /* src/ORBmatcher.cc:38 */
 #include "_ref/Frame_grid.inc"
 #include "_ref/MapPoint_ComputeDistinctiveDescriptors.inc"
 #include "_ref/ORBmatcher_SearchByProjection.inc"
+#include "_ref/ORBmatcher_SearchForInitialization.inc"
 
 /* protected members of the extractor, for the stage-level comparisons */
 struct Probe : ORBextractor {
@@ -411,6 +413,31 @@ int ref_search_by_projection(const orc_keypoint* kps, const uint8_t* desc, int n
     ORBmatcher matcher(nnratio, true);
     const int nm = matcher.SearchByProjection(F, vp, th, false, 50.0f);
     for (int i = 0; i < n; i++) owner[i] = !F.mvpMapPoints[i] ? -1 : F.mvpMapPoints[i] == &initial ? -2 : (int32_t)(F.mvpMapPoints[i] - store.data());
+    return nm;
+}
+
+/* ORBmatcher::SearchForInitialization (src/ORBmatcher.cc:706-821) on two frames given as arrays (kps = mvKeysUn), F2's grid built by the
+ * reference's own AssignFeaturesToGrid.  prev_matched [n1][2] in/out, matches12 [n1] out.  Returns nmatches. */
+int ref_search_for_initialization(const orc_keypoint* kps1, const uint8_t* desc1, int n1, const orc_keypoint* kps2, const uint8_t* desc2, int n2,
+                                  const float* grid4, float* prev_matched, int window, float nnratio, int check_orientation, int32_t* matches12) {
+    using namespace ORB_SLAM3;
+    ArenaScope scope;
+    Frame F1, F2;
+    Frame::mnMinX = grid4[0]; Frame::mnMinY = grid4[1]; Frame::mfGridElementWidthInv = grid4[2]; Frame::mfGridElementHeightInv = grid4[3];
+    F1.N = n1; F2.N = n2;
+    F1.mDescriptors = cv::Mat(n1, 32, CV_8UC1, (void*)desc1, 32);
+    F2.mDescriptors = cv::Mat(n2, 32, CV_8UC1, (void*)desc2, 32);
+    F1.mvKeysUn.resize(n1); F2.mvKeysUn.resize(n2);
+    if (n1) std::memcpy((void*)F1.mvKeysUn.data(), kps1, sizeof(orc_keypoint) * n1);
+    if (n2) std::memcpy((void*)F2.mvKeysUn.data(), kps2, sizeof(orc_keypoint) * n2);
+    F1.mvKeys = F1.mvKeysUn; F2.mvKeys = F2.mvKeysUn;
+    F2.AssignFeaturesToGrid();
+    std::vector<cv::Point2f> prev(n1);
+    for (int i = 0; i < n1; i++) prev[i] = cv::Point2f(prev_matched[2 * i], prev_matched[2 * i + 1]);
+    std::vector<int> m12;
+    ORBmatcher matcher(nnratio, check_orientation != 0);
+    const int nm = matcher.SearchForInitialization(F1, F2, prev, m12, window);
+    for (int i = 0; i < n1; i++) { matches12[i] = m12[i]; prev_matched[2 * i] = prev[i].x; prev_matched[2 * i + 1] = prev[i].y; }
     return nm;
 }
 

@@ -655,7 +655,9 @@ __global__ void __launch_bounds__(FAST_NT, 8) k_fast_cells_list(const __grid_con
 }
 
 /* ---- streaming detector: the iniTh pass over whole levels ------------------------------------------------------ */
+#ifndef FS_WARPS
 #define FS_WARPS 1
+#endif
 #define FS_R 8          /* rows per compaction chunk */
 #define FS_COLS 120     /* candidate columns per strip (lanes 1..30; lanes 0 and 31 carry the 4 px halos) */
 
@@ -668,7 +670,7 @@ __global__ void __launch_bounds__(FAST_NT, 8) k_fast_cells_list(const __grid_con
  * k_fast_nms then does the cell-local non-maximum suppression and ordering. */
 #define FS_BROWS (FS_R + 6)   /* rows yc-3 .. yc+FS_R+2 of the current chunk */
 #define FS_PW 33               /* words per buffered row: 32 + 1 so that equal columns of different rows hit different banks */
-__global__ void __launch_bounds__(FS_WARPS * 32, 32) k_fast_stream(const __grid_constant__ ExDesc d, ExBuffers b, int stripBase, int nStrips) {
+__global__ void __launch_bounds__(FS_WARPS * 32, 32 / FS_WARPS) k_fast_stream(const __grid_constant__ ExDesc d, ExBuffers b, int stripBase, int nStrips) {
     __shared__ __align__(16) uint32_t s_buf[FS_WARPS][FS_BROWS][FS_PW];
     __shared__ uint16_t s_q[FS_WARPS][FS_R * FS_COLS + 32];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -788,7 +790,9 @@ __global__ void __launch_bounds__(FS_WARPS * 32, 32) k_fast_stream(const __grid_
  * keep the strict local maxima (cv::FAST nonmaxSuppression: neighbours outside the cell's candidate area or below the
  * threshold count as 0), write them in (y, x) order.  A cell that ends up empty is queued for the minTh fallback
  * (k_fast_cells_list). */
+#ifndef FN_WARPS
 #define FN_WARPS 1
+#endif
 #define FN_TP 72
 __global__ void __launch_bounds__(FN_WARPS * 32) k_fast_nms(const __grid_constant__ ExDesc d, ExBuffers b) {
     __shared__ __align__(16) uint8_t s_scAll[FN_WARPS][FN_TP * 80];   /* (ch+2) rows x tp <= 72 x 80 */

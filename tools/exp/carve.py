@@ -5,6 +5,7 @@ import numpy as np, torch
 import bench
 from orb_slam3_detailed_comments_kor_b200 import ORBextractor, _lib
 from orb_slam3_detailed_comments_kor_b200 import matcher as M
+if os.environ.get('ORBFE_EXP_LIB'): _lib.LIB_PATH = os.environ['ORBFE_EXP_LIB']
 bench.set_workload("euroc")
 W, H, PARAMS, LAP, MBF, FX = bench.W, bench.H, bench.PARAMS, bench.LAP, bench.MBF, bench.FX
 P = 256
