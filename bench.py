@@ -909,6 +909,52 @@ def main():
                   "ms_per_step": pj_ms, "frames_per_step": PF * world, "keypoints_per_frame": 1200, "map_points_per_frame": int(pj_qoff[1]),
                   "accepted_per_step": pj_acc, "note": "ORBmatcher::SearchByProjection(Frame&, vpMapPoints, th=1) incl. the frame grid; device resident"}
 
+    # ---- ORBmatcher::SearchForInitialization: pairs of frames from the initial extractor (5 x nFeatures keypoints, of
+    #      which about 22 % are on level 0 and take part), window 100 px, one CTA per pair
+    def init_case(seed, n=5 * PARAMS[0], clusters=150, noise=20):
+        rng = np.random.RandomState(seed)
+        centres = rng.randint(0, 256, (clusters, 32)).astype(np.uint8)
+        def frame():
+            k = np.zeros(n, _lib.KP_DTYPE)
+            k["x"], k["y"] = rng.uniform(0, W, n).astype(np.float32), rng.uniform(0, H, n).astype(np.float32)
+            k["octave"] = np.where(rng.rand(n) < 0.22, 0, rng.randint(1, 8, n))
+            k["angle"] = rng.uniform(0, 40, n).astype(np.float32)
+            flip = np.zeros((n, 256), np.uint8)
+            for i, m in enumerate(rng.randint(0, noise + 1, n)):
+                flip[i, rng.randint(0, 256, m)] = 1
+            return k, centres[rng.randint(0, clusters, n)] ^ np.packbits(flip, axis=1, bitorder="little")
+        (k1, d1), (k2, d2) = frame(), frame()
+        return k1, d1, k2, d2, PJ.frame_grid(0, W, 0, H), np.stack([k1["x"], k1["y"]], 1).astype(np.float32)
+    in_cases = [init_case(700 + i) for i in range(8)]
+    IP = 148
+    in_order = [in_cases[i % 8] for i in range(IP)]
+    in_o1 = np.cumsum([0] + [len(c[0]) for c in in_order]).astype(np.int32)
+    in_o2 = np.cumsum([0] + [len(c[2]) for c in in_order]).astype(np.int32)
+    in_d = [to_dev(np.concatenate([c[i] for c in in_order])) for i in range(4)] + [to_dev(np.stack([c[4] for c in in_order])), to_dev(in_o1), to_dev(in_o2)]
+    in_prev0 = to_dev(np.concatenate([c[5] for c in in_order]))
+    in_prev = in_prev0.clone()
+    in_m = torch.zeros(int(in_o1[-1]), dtype=torch.int32, device="cuda")
+    in_nm, in_rounds = torch.zeros(IP, dtype=torch.int32, device="cuda"), torch.zeros(IP, dtype=torch.int32, device="cuda")
+
+    def in_step():
+        in_prev.copy_(in_prev0, non_blocking=True)                        # vbPrevMatched is updated in place: every step starts from the same one
+        PJ.search_for_initialization_device(IP, in_d[0].data_ptr(), in_d[1].data_ptr(), in_d[5].data_ptr(), in_d[2].data_ptr(), in_d[3].data_ptr(), in_d[6].data_ptr(),
+                                            in_d[4].data_ptr(), in_prev.data_ptr(), in_m.data_ptr(), in_nm.data_ptr(), 100, 0.9, True, 50, in_rounds.data_ptr(),
+                                            device=local_rank, stream=st)
+    for _ in range(3):
+        in_step()
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        in_step()
+    e1.record()
+    barrier()
+    in_ms = max_over_ranks(e0.elapsed_time(e1) / args.steps)
+    initialization = {"value": IP * world / (in_ms / 1e3), "unit": "frame_pairs/s", "ms_per_step": in_ms, "pairs_per_step": IP * world,
+                      "keypoints_per_frame": 5 * PARAMS[0], "level0_keypoints_per_frame": int((in_cases[0][0]["octave"] == 0).sum()),
+                      "matches_per_pair": float(in_nm.float().mean().item()), "rounds_max": int(in_rounds.max().item()),
+                      "note": "ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, 100) incl. F2's grid; device resident"}
+
     # ---- bag-of-words assignment: Frame::ComputeBoW on the left frames the extractor just produced (device
     #      buffers chained), ORBvoc-shaped synthetic vocabulary (k = 10, L = 6, 1.1 M nodes, TF-IDF, L1)
     from orb_slam3_detailed_comments_kor_b200.bow import ORBVocabulary
@@ -977,6 +1023,14 @@ def main():
             list(tp.map(lambda i: ovoc.transform(bsample[i % 8], 4), range(8 * cores)))
         bdt = time.perf_counter() - t0
         cpu["bow"] = {"value": 8 * cores / bdt, "unit": "frames/s", "sample": "%d frames (%.2f s wall) frame-parallel over %d threads" % (8 * cores, bdt, cores)}
+        from oracle import ref_oracle as _RO
+        init_fn = _RO.search_for_initialization if reference_available() else O.search_for_initialization
+        t0 = time.perf_counter()
+        with ThreadPoolExecutor(cores) as tp:
+            list(tp.map(lambda i: init_fn(*in_cases[i % 8][:6], 100, 0.9, True), range(4 * cores)))
+        idt = time.perf_counter() - t0
+        cpu["initialization"] = {"value": 4 * cores / idt, "unit": "frame_pairs/s", "kind": "reference" if reference_available() else "port",
+                                 "sample": "%d pairs (%.2f s wall) pair-parallel over %d threads" % (4 * cores, idt, cores)}
         cpu["projection"] = {"value": reps * int(pj_qoff[1]) / pdt, "unit": "map_point_searches/s",
                              "sample": "%d frames (%.2f s wall) frame-parallel over %d threads" % (reps, pdt, cores)}
 
@@ -991,7 +1045,7 @@ def main():
                                        "ExtractORB threads), blur beside quadtree + assemble, ComputeStereoMatches behind both; timed by events on the caller's stream",
                            "serial_ms_per_step": ms_serial},
                 "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
-                "single_frame_latency_ms": single_ms, "shim_single_frame_latency_ms": shim_ms, "rectify": rectify, "projection": projection, "bow": bow,
+                "single_frame_latency_ms": single_ms, "shim_single_frame_latency_ms": shim_ms, "rectify": rectify, "projection": projection, "initialization": initialization, "bow": bow,
                 "gpu_launches": (2 * (PARAMS[2] + 8) + 3) * args.steps,
                 "hamming": hamming}
         print(json.dumps(line), flush=True)

@@ -460,6 +460,23 @@ int orbfe_search_by_projection(int device, const orbfe_keypoint* kps, const uint
                                const uint8_t* qdesc, int nq, int th_high, float nnratio, int check_orientation,
                                const float* inv_level_sigma2, orbfe_proj_match* out, int* nmatches);
 
+/* Replaces int ORBmatcher::SearchForInitialization(Frame &F1, Frame &F2, vector<cv::Point2f> &vbPrevMatched, vector<int> &vnMatches12,
+ * int windowSize) (src/ORBmatcher.cc:706-821; caller Tracking::MonocularInitialization, src/Tracking.cc:2462, with windowSize 100 and
+ * ORBmatcher(0.9, true)) for a batch of frame pairs on the device.  kps1 / kps2 are F1.mvKeysUn / F2.mvKeysUn (pt, octave >= 0 and angle
+ * are read), pair p = rows [d_off1[p], d_off1[p+1]) and [d_off2[p], d_off2[p+1]), at most 8192 rows per frame (a pair with more gets
+ * nmatches = -1 and is not searched); d_grids[p] is F2's grid geometry; d_prev_matched [rows of F1][2] is vbPrevMatched, read and
+ * updated (:816-818); d_matches12 [rows of F1] receives vnMatches12, d_nmatches[p] the return value; d_rounds (may be NULL) the number of
+ * rounds the kernel needed.  th_low = ORBmatcher::TH_LOW (50).  The result is the reference's, including the order dependence of
+ * vMatchedDistance (:745) and of the displaced matches (:764-768).  Asynchronous on `stream`, no allocation. */
+int orbfe_search_for_initialization_device(int device, int npairs, const orbfe_keypoint* d_kps1, const uint8_t* d_desc1, const int32_t* d_off1,
+                                           const orbfe_keypoint* d_kps2, const uint8_t* d_desc2, const int32_t* d_off2, const orbfe_frame_grid* d_grids,
+                                           float* d_prev_matched, int window, float nnratio, int check_orientation, int th_low, int32_t* d_matches12,
+                                           int32_t* d_nmatches, int32_t* d_rounds, void* stream);
+/* One pair over host memory (copies inside, synchronous). */
+int orbfe_search_for_initialization(int device, const orbfe_keypoint* kps1, const uint8_t* desc1, int n1, const orbfe_keypoint* kps2, const uint8_t* desc2, int n2,
+                                    const orbfe_frame_grid* grid, float* prev_matched, int window, float nnratio, int check_orientation, int th_low,
+                                    int32_t* matches12, int* nmatches);
+
 /* ------------------------------------------------------------------------------------------ input conditioning */
 /* The steps the example drivers and Tracking run on each image before the extractor, so that an
  * uploaded frame can stay on the GPU.  Bit-exact with OpenCV 4.13's 8-bit fixed-point paths. */

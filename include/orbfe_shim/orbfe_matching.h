@@ -107,6 +107,33 @@ inline int SearchByProjection(const std::vector<cv::KeyPoint>& keys, const cv::M
     return nmatches;
 }
 
+/* Body of ORBmatcher::SearchForInitialization(Frame &F1, Frame &F2, vector<cv::Point2f> &vbPrevMatched, vector<int> &vnMatches12,
+ * int windowSize) (src/ORBmatcher.cc:706-821), a drop-in: keys1 / descriptors1 = F1.mvKeysUn / F1.mDescriptors, likewise for F2;
+ * the four grid numbers are Frame's static members.  vbPrevMatched is updated as the reference does (:816-818).
+ * Inside ORBmatcher::SearchForInitialization the whole body becomes
+ *     return ORB_SLAM3::orbfe::SearchForInitialization(F1.mvKeysUn, F1.mDescriptors, F2.mvKeysUn, F2.mDescriptors, Frame::mnMinX, Frame::mnMinY,
+ *                Frame::mfGridElementWidthInv, Frame::mfGridElementHeightInv, vbPrevMatched, vnMatches12, windowSize, mfNNratio, mbCheckOrientation, TH_LOW); */
+inline int SearchForInitialization(const std::vector<cv::KeyPoint>& keys1, const cv::Mat& descriptors1, const std::vector<cv::KeyPoint>& keys2,
+                                   const cv::Mat& descriptors2, float mnMinX, float mnMinY, float mfGridElementWidthInv, float mfGridElementHeightInv,
+                                   std::vector<cv::Point2f>& vbPrevMatched, std::vector<int>& vnMatches12, int windowSize, float mfNNratio,
+                                   bool checkOrientation, int thLow = 50, int device = 0) {
+    static_assert(sizeof(cv::KeyPoint) == sizeof(orbfe_keypoint), "cv::KeyPoint layout");
+    static_assert(sizeof(cv::Point2f) == 2 * sizeof(float), "cv::Point2f layout");
+    const int n1 = (int)keys1.size(), n2 = (int)keys2.size();
+    vnMatches12.assign(n1, -1);
+    std::vector<unsigned char> d1((size_t)n1 * 32), d2((size_t)n2 * 32);
+    for (int i = 0; i < n1; i++) std::memcpy(&d1[(size_t)i * 32], descriptors1.ptr<unsigned char>(i), 32);
+    for (int i = 0; i < n2; i++) std::memcpy(&d2[(size_t)i * 32], descriptors2.ptr<unsigned char>(i), 32);
+    const orbfe_frame_grid grid = {mnMinX, mnMinY, mfGridElementWidthInv, mfGridElementHeightInv};
+    int nmatches = 0;
+    if (orbfe_search_for_initialization(device, reinterpret_cast<const orbfe_keypoint*>(keys1.data()), d1.data(), n1,
+                                        reinterpret_cast<const orbfe_keypoint*>(keys2.data()), d2.data(), n2, &grid,
+                                        reinterpret_cast<float*>(vbPrevMatched.data()), windowSize, mfNNratio, checkOrientation ? 1 : 0, thLow,
+                                        vnMatches12.data(), &nmatches) != ORBFE_OK)
+        throw std::runtime_error(std::string("orbfe_search_for_initialization: ") + orbfe_last_error());
+    return nmatches;
+}
+
 }  // namespace orbfe
 }  // namespace ORB_SLAM3
 #endif

@@ -6,7 +6,7 @@ import sys
 _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
 LIB = os.path.join(_HERE, "liborbfe.so")
-SOURCES = ["orbfe_host.cu", "orbfe_extract.cu", "orbfe_match.cu", "orbfe_condition.cu", "orbfe_project.cu", "orbfe_bow.cu"]
+SOURCES = ["orbfe_host.cu", "orbfe_extract.cu", "orbfe_match.cu", "orbfe_condition.cu", "orbfe_project.cu", "orbfe_bow.cu", "orbfe_init.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "--fmad=false",
               "-Xcompiler", "-fPIC,-Wall,-Wno-unused-function,-Wno-unknown-pragmas", "-shared", "-cudart", "static", "-ldl"] + os.environ.get("ORBFE_EXTRA_NVCC", "").split()
 

@@ -64,3 +64,28 @@ def search_by_projection_device(nframes, max_keypoints, d_kps, d_desc, d_kp_offs
                                                        vp(d_q_offsets), th_high, C.c_float(nnratio), int(check_orientation), vp(d_inv_level_sigma2), vp(d_out),
                                                        vp(d_taken_out),
                                                        vp(stream)))
+
+
+def search_for_initialization(kps1, desc1, kps2, desc2, grid, prev_matched, window=100, nnratio=0.9, check_orientation=True, th_low=50, device=0):
+    """ORBmatcher::SearchForInitialization (src/ORBmatcher.cc:706-821), one pair, host arrays.
+    Returns (vnMatches12, vbPrevMatched afterwards, nmatches)."""
+    kps1, kps2 = np.ascontiguousarray(kps1, KP_DTYPE), np.ascontiguousarray(kps2, KP_DTYPE)
+    desc1, desc2 = np.ascontiguousarray(desc1, np.uint8), np.ascontiguousarray(desc2, np.uint8)
+    grid = np.ascontiguousarray(grid, np.float32)
+    n1, n2 = kps1.shape[0], kps2.shape[0]
+    assert desc1.shape == (n1, 32) and desc2.shape == (n2, 32) and grid.shape == (4,)
+    prev = np.array(prev_matched, np.float32).reshape(n1, 2).copy()
+    m12 = np.full(n1, -1, np.int32)
+    nm = C.c_int(0)
+    check(_lib.lib().orbfe_search_for_initialization(device, ptr(kps1), ptr(desc1), n1, ptr(kps2), ptr(desc2), n2, ptr(grid), ptr(prev), int(window),
+                                                     C.c_float(nnratio), int(check_orientation), int(th_low), ptr(m12), C.byref(nm)))
+    return m12, prev, nm.value
+
+
+def search_for_initialization_device(npairs, d_kps1, d_desc1, d_off1, d_kps2, d_desc2, d_off2, d_grids, d_prev_matched, d_matches12, d_nmatches,
+                                     window=100, nnratio=0.9, check_orientation=True, th_low=50, d_rounds=None, device=0, stream=None):
+    """A batch of frame pairs, device pointers (ints), asynchronous on `stream`."""
+    vp = lambda p: C.c_void_p(p) if p else None  # noqa: E731
+    check(_lib.lib().orbfe_search_for_initialization_device(device, npairs, vp(d_kps1), vp(d_desc1), vp(d_off1), vp(d_kps2), vp(d_desc2), vp(d_off2),
+                                                            vp(d_grids), vp(d_prev_matched), int(window), C.c_float(nnratio), int(check_orientation),
+                                                            int(th_low), vp(d_matches12), vp(d_nmatches), vp(d_rounds), vp(stream)))

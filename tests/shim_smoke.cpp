@@ -91,10 +91,17 @@ int main(int argc, char** argv) {
     const int proj = orbfe::SearchByProjection(kL, dL, -1, &uR, nullptr, taken, 0.f, 0.f, 64.f / W, 48.f / H, pq, dL, 0.8f, pm);
     int projSelf = 0;
     for (size_t i = 0; i < pm.size(); i++) projSelf += pm[i].accepted && pm[i].best_idx == (int)i;
+    // Tracking::MonocularInitialization-like (src/Tracking.cc:2462): the left keypoints against the right ones, previous matches = own positions
+    std::vector<cv::Point2f> prevMatched(kL.size());
+    for (size_t i = 0; i < kL.size(); i++) prevMatched[i] = kL[i].pt;
+    std::vector<int> ini12;
+    const int ini = orbfe::SearchForInitialization(kL, dL, kR, dR, 0.f, 0.f, 64.f / W, 48.f / H, prevMatched, ini12, 100, 0.9f, true, ORBmatcher::TH_LOW);
+    int iniCount = 0;
+    for (int v : ini12) iniCount += v >= 0;
     cv::Mat empty;
     const int rcEmpty = left(empty, mask, kR, dR, lap);
-    printf("shim n=%zu mono=%d monoR=%d levels=%d pyr0=%dx%d stereo=%d d01=%d top2acc=%d proj=%d projself=%d empty=%d first=(%.1f,%.1f,%.3f,%d)\n",
-           kL.size(), monoL, monoR, left.GetLevels(), left.mvImagePyramid[0].cols, left.mvImagePyramid[0].rows, matched, d01, acc, proj, projSelf, rcEmpty,
+    printf("shim n=%zu mono=%d monoR=%d levels=%d pyr0=%dx%d stereo=%d d01=%d top2acc=%d proj=%d projself=%d init=%d initcount=%d empty=%d first=(%.1f,%.1f,%.3f,%d)\n",
+           kL.size(), monoL, monoR, left.GetLevels(), left.mvImagePyramid[0].cols, left.mvImagePyramid[0].rows, matched, d01, acc, proj, projSelf, ini, iniCount, rcEmpty,
            kL[0].pt.x, kL[0].pt.y, kL[0].angle, kL[0].octave);
     return 0;
 }

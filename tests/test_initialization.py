@@ -111,3 +111,56 @@ def test_oracle_hand_cases():
     d1[1, 0] = 0
     m, p, nm = O.search_for_initialization(k1, d1, k2, d2, g, prev, 100, 0.9, False)
     assert list(m) == [0, -1] and nm == 1
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", sorted(RANDOM_CASES))
+@pytest.mark.parametrize("window,ratio,ori", [(100, 0.9, True), (30, 0.9, False), (100, 0.6, True)])
+def test_gpu_equals_oracle_random(name, window, ratio, ori):
+    from orb_slam3_detailed_comments_kor_b200 import projection as P
+    k1, d1, k2, d2, g, prev = random_case(**RANDOM_CASES[name])
+    m, p, nm = O.search_for_initialization(k1, d1, k2, d2, g, prev, window, ratio, ori)
+    gm, gp, gnm = P.search_for_initialization(k1, d1, k2, d2, g, prev, window, ratio, ori)
+    assert gnm == nm and np.array_equal(gm, m) and np.array_equal(gp, p)
+
+
+@pytest.mark.gpu
+def test_gpu_batch_of_pairs_on_the_device_and_limits():
+    """Several pairs in one launch (extracted frames, random ones, an empty frame, one beyond the row limit), results per pair as the
+    oracle's; the second call with the updated vbPrevMatched; rounds reported."""
+    import torch
+    from orb_slam3_detailed_comments_kor_b200 import projection as P
+    from orb_slam3_detailed_comments_kor_b200._lib import OrbfeError
+    cases = [extracted_case(31), random_case(**RANDOM_CASES["dense_conflicts"]), random_case(seed=9, n1=0, n2=50), random_case(seed=10, n1=60, n2=0),
+             random_case(seed=11, n1=8192, n2=8192, clusters=80, noise=14, level0=0.5), random_case(seed=12, n1=8193, n2=10), extracted_case(32, nfeatures=5000)]
+    off1 = np.cumsum([0] + [len(c[0]) for c in cases]).astype(np.int32)
+    off2 = np.cumsum([0] + [len(c[2]) for c in cases]).astype(np.int32)
+    cat = lambda i, dt: np.ascontiguousarray(np.concatenate([np.asarray(c[i]).reshape(len(c[i]), -1) if dt is None else c[i] for c in cases]))  # noqa: E731
+    k1 = np.concatenate([c[0] for c in cases]); d1 = np.concatenate([c[1] for c in cases])
+    k2 = np.concatenate([c[2] for c in cases]); d2 = np.concatenate([c[3] for c in cases])
+    grids = np.stack([c[4] for c in cases]); prev = np.concatenate([c[5] for c in cases]).astype(np.float32)
+    dev = lambda a: torch.from_numpy(np.ascontiguousarray(a).view(np.uint8).reshape(-1)).cuda()  # noqa: E731
+    t_k1, t_d1, t_k2, t_d2, t_o1, t_o2, t_g, t_prev = dev(k1), dev(d1), dev(k2), dev(d2), dev(off1), dev(off2), dev(grids), dev(prev)
+    t_m = torch.full((len(k1),), -7, dtype=torch.int32, device="cuda")
+    t_nm = torch.zeros(len(cases), dtype=torch.int32, device="cuda")
+    t_rounds = torch.zeros(len(cases), dtype=torch.int32, device="cuda")
+    for call in range(2):
+        P.search_for_initialization_device(len(cases), t_k1.data_ptr(), t_d1.data_ptr(), t_o1.data_ptr(), t_k2.data_ptr(), t_d2.data_ptr(), t_o2.data_ptr(),
+                                           t_g.data_ptr(), t_prev.data_ptr(), t_m.data_ptr(), t_nm.data_ptr(), 100, 0.9, True, 50, t_rounds.data_ptr())
+        torch.cuda.synchronize()
+        gm, gnm, gprev = t_m.cpu().numpy(), t_nm.cpu().numpy(), t_prev.cpu().numpy().view(np.float32).reshape(-1, 2)
+        rounds = t_rounds.cpu().numpy()
+        for i, c in enumerate(cases):
+            a, b = off1[i], off1[i + 1]
+            if len(c[0]) > 8192:
+                assert gnm[i] == -1
+                continue
+            m, p, nm = O.search_for_initialization(c[0], c[1], c[2], c[3], c[4], prev[a:b], 100, 0.9, True)
+            assert gnm[i] == nm, "call %d pair %d" % (call, i)
+            assert np.array_equal(gm[a:b], m) and np.array_equal(gprev[a:b], p), "call %d pair %d" % (call, i)
+            prev[a:b] = p
+        assert rounds[0] >= 1 and rounds[4] >= 2
+        print("rounds per pair:", rounds.tolist(), "matches:", gnm.tolist())
+    with pytest.raises(OrbfeError):
+        c = cases[5]
+        P.search_for_initialization(c[0], c[1], c[2], c[3], c[4], c[5])

@@ -69,5 +69,7 @@ def test_shim_matches_oracle(tmp_path):
     pm, _, nm = O.search_by_projection(kL, dL, pq, dL, grid, u_right=u, nnratio=0.8)
     assert int(f["proj"]) == nm and int(f["projself"]) == int(((pm["best_idx"] == np.arange(len(kL))) & (pm["accepted"] == 1)).sum())
     assert nm > 1000
+    im, _, inm = O.search_for_initialization(kL, dL, kR, dR, grid, np.stack([kL["x"], kL["y"]], 1), 100, 0.9, True)
+    assert int(f["init"]) == inm and int(f["initcount"]) == int((im >= 0).sum()) and inm > 10
     first = "(%.1f,%.1f,%.3f,%d)" % (kL[0]["x"], kL[0]["y"], kL[0]["angle"], kL[0]["octave"])
     assert f["first"] == first

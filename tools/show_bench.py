@@ -18,3 +18,4 @@ for l in sys.stdin:
     print("clocks", d.get("clocks"), "cpu", d.get("cpu_baseline"))
     print("projection", d.get("projection"), "| rectify %.0f frames/s" % (d.get("rectify") or {}).get("value", 0))
     print("bow", d.get("bow"))
+    print("initialization", d.get("initialization"), "| serial step ms", (d.get("config") or {}).get("serial_ms_per_step"))
