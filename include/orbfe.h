@@ -477,6 +477,12 @@ int orbfe_search_for_initialization(int device, const orbfe_keypoint* kps1, cons
                                     const orbfe_frame_grid* grid, float* prev_matched, int window, float nnratio, int check_orientation, int th_low,
                                     int32_t* matches12, int* nmatches);
 
+/* Host-only self check (no device needed): rBRIEF's rotation uses cosf / sinf of the host libm in the reference
+ * (src/ORBextractor.cc:110-111); the device evaluates them in double and corrects the 96 binary32 angles where that moves a tap with a
+ * table of glibc 2.39 (x86-64) values.  Returns how many of the table's entries this host's libm does NOT reproduce (0: descriptors equal
+ * this host's own CPU build for every possible angle); *listed (may be NULL) receives the table size. */
+int orbfe_check_host_libm(int* listed);
+
 /* ------------------------------------------------------------------------------------------ input conditioning */
 /* The steps the example drivers and Tracking run on each image before the extractor, so that an
  * uploaded frame can stay on the GPU.  Bit-exact with OpenCV 4.13's 8-bit fixed-point paths. */

@@ -13,6 +13,8 @@
  * All frames of a batch go through one launch per stage (gridDim.y / .z = frame); frames never interact.
  * Integer stages are bit-exact by construction; float stages use round-to-nearest intrinsics so that no FMA
  * contraction can change a bit relative to the oracle (built with -ffp-contract=off). */
+#include <math.h>
+#include <string.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -1388,6 +1390,29 @@ int orbfe_upload_constants(const int* umax16, const int8_t* pattern1024) {
     ORBFE_CUDA(cudaMemcpyToSymbol(g_icw, icw, sizeof icw));
     ORBFE_CUDA(orbfe_trig_init());
     return 0;
+}
+
+/* Host only, no device needed.  The 96 angles of orbfe_trig_exceptions.inc carry the cosf / sinf of glibc 2.39 (x86-64); a host whose
+ * libm rounds those differently would see its own CPU build of the reference disagree with this library on a tap of such a keypoint.
+ * Returns how many of the listed (angle, cosf, sinf) triples this host's libm does not reproduce (0 = the table is this host's). */
+extern "C" int orbfe_check_host_libm(int* listed) {
+    static const OrbfeTrigEx host_table[] = {
+#include "orbfe_trig_exceptions.inc"
+    };
+    const float factorPI = (float)(3.14159265358979323846 / 180.0);   /* src/ORBextractor.cc:104 */
+    int bad = 0, n = 0;
+    for (const OrbfeTrigEx& e : host_table) {
+        float angle, c, s;
+        memcpy(&angle, &e.angle, 4);
+        volatile float x = angle * factorPI;
+        c = cosf(x); s = sinf(x);
+        uint32_t cb, sb;
+        memcpy(&cb, &c, 4); memcpy(&sb, &s, 4);
+        bad += (cb != e.c || sb != e.s) ? 1 : 0;
+        n++;
+    }
+    if (listed) *listed = n;
+    return bad;
 }
 
 int orbfe_quadtree_smem_bytes(int cap) {

@@ -61,3 +61,13 @@ def test_host_merge_rule():
     out = merge_top2_host(parts, 50, 0.9, False)
     assert tuple(out[0]) == (10, 10, 5, 0)      # tie on best1 -> lowest shard keeps idx; second = the other 10
     assert tuple(out[1]) == (40, 41, 130, 0)    # 40 < 0.9*41 = 36.9 is false
+
+
+def test_host_libm_reproduces_the_trig_exception_table():
+    """The 96 rotation angles whose cosf / sinf the device takes from a table: on this host (the image's glibc) the table must be the
+    libm's own values; elsewhere the count says how many angles can differ from that host's CPU build."""
+    import ctypes as C
+    L = _lib.lib()
+    n = C.c_int(0)
+    assert L.orbfe_check_host_libm(C.byref(n)) == 0
+    assert n.value == 96
