@@ -457,21 +457,20 @@ def run_workload(args, wl, rank, world, local_rank, barrier, max_over_ranks):
     hLn, hRn = hL.numpy(), hR.numpy()
     subs = list(range(0, P, SUB))
     if fisheye:
-        outs = [out_set()]
-        h_match = torch.empty((SUB, cap), dtype=torch.int32, pin_memory=True)
-        h_depth = torch.empty((SUB, cap), dtype=torch.float32, pin_memory=True)
-        call = "orbfe_extract_batch_host x 2 + orbfe_fisheye_match_batch_device + orbfe_fisheye_triangulate_batch_device + download of matches and depths (synchronous)"
+        pin = lambda shape, dt: torch.empty(shape, dtype=dt, pin_memory=True).numpy()  # noqa: E731
+        fish_set = lambda: out_set()[:8] + (pin((SUB, cap), torch.int32), pin((SUB, cap), torch.int32), pin((SUB, cap), torch.float32), pin((SUB, cap, 3), torch.float32))  # noqa: E731
+        outs = [fish_set(), fish_set()]
+        rig = M.make_fisheye_rig(cam1, cam2, np.array(Rlr, np.float32).reshape(3, 3), tlr)
+        call = "orbfe_fisheye_frames_submit / orbfe_stereo_frames_wait, two sub-batches in flight (keypoints, descriptors, both match vectors, depths and 3-D points out)"
 
         def e2e_run(nsteps):
-            for _ in range(nsteps):
-                for s0 in subs:
-                    exL.extract_batch_host(hLn[s0:s0 + SUB], LAP, outs[0][0:4])
-                    exR.extract_batch_host(hRn[s0:s0 + SUB], LAP, outs[0][4:8])
-                    match(st)
-                    h_match.copy_(d_match, non_blocking=True)
-                    h_depth.copy_(d_depth, non_blocking=True)
-                    torch.cuda.synchronize()
-        d2h = 2 * P * (cap * 60 + 8) + 2 * P * cap * 4
+            seq = [s0 for _ in range(nsteps) for s0 in subs]
+            M.fisheye_frames_submit(exL, exR, hLn[seq[0]:seq[0] + SUB], hRn[seq[0]:seq[0] + SUB], rig, 0.7, LAP, outs[0])
+            for k in range(1, len(seq)):
+                M.fisheye_frames_submit(exL, exR, hLn[seq[k]:seq[k] + SUB], hRn[seq[k]:seq[k] + SUB], rig, 0.7, LAP, outs[k & 1])
+                M.fisheye_frames_wait(exL, exR, outs[(k - 1) & 1])
+            M.fisheye_frames_wait(exL, exR, outs[(len(seq) - 1) & 1])
+        d2h = 2 * P * (cap * 60 + 8) + P * cap * (4 + 4 + 4 + 12)
     else:
         outs = [out_set(), out_set()]
         call = "orbfe_stereo_frames_submit / _wait, two sub-batches in flight"

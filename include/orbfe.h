@@ -273,6 +273,14 @@ int orbfe_fisheye_triangulate_batch_device(orbfe_extractor* exL, orbfe_extractor
 /* KannalaBrandt8::TriangulateMatches (src/CameraModels/KannalaBrandt8.cpp:338-407) for n keypoint pairs given as plain device arrays:
  * d_uv1 / d_uv2 [n][2] pixel coordinates in camera 1 / 2, d_sigma1 / d_sigma2 [n] = mvLevelSigma2 of their octaves;
  * d_depth[i] = the function's return value (-1 when it rejects the pair), d_p3d [n][3] = p3D.  Asynchronous on `stream`. */
+/* Frame's fisheye-rig constructor (src/Frame.cc:1023-1101) for a batch of pairs from host memory, the pipelined counterpart of
+ * orbfe_stereo_frames_submit: uploads, both extractions with the lapping interval, ComputeStereoFishEyeMatches (knn-2 + ratio 0.7 in the
+ * reference, TriangulateMatches, the depth test) and the downloads overlap chunk by chunk; at most two batches in flight, collected
+ * in order by orbfe_stereo_frames_wait.  match_lr / match_rl / depth [nframes*cap] = mvLeftToRightMatch / mvRightToLeftMatch (right
+ * rows) / mvDepth, p3d [nframes*cap*3] = mvStereo3Dpoints; any output pointer may be NULL; pinned host memory keeps the copies async. */
+int orbfe_fisheye_frames_submit(orbfe_extractor* exL, orbfe_extractor* exR, const uint8_t* h_left, const uint8_t* h_right, int nframes, int lap0, int lap1,
+                                const orbfe_fisheye_rig* rig, double ratio, orbfe_keypoint* kps_l, uint8_t* desc_l, orbfe_keypoint* kps_r, uint8_t* desc_r, int cap,
+                                int32_t* match_lr, int32_t* match_rl, float* depth, float* p3d);
 int orbfe_kb8_triangulate_pairs_device(int device, const orbfe_fisheye_rig* rig, const float* d_uv1, const float* d_uv2, const float* d_sigma1,
                                        const float* d_sigma2, int n, float* d_depth, float* d_p3d, void* stream);
 

@@ -52,9 +52,22 @@ __global__ void __launch_bounds__(256) k_pyramid_copy0(const __grid_constant__ E
     uint8_t* dst = b.pyr + f * d.pyrSlab + L.pyrOff + (size_t)(row + ORBFE_EDGE) * L.pitch + ORBFE_ROW_LEAD + px0;
     if (px0 + 16 <= L.w && ((reinterpret_cast<uintptr_t>(src) & 15) == 0)) {
         *reinterpret_cast<uint4*>(dst) = __ldg(reinterpret_cast<const uint4*>(src));
-    } else {
-        for (int k = 0; k < 16 && px0 + k < L.w; k++) dst[k] = __ldg(src + k);
+        return;
     }
+    if (px0 + 16 <= L.w) {
+        /* odd widths (KITTI: 1241) leave most rows unaligned: five aligned words around the chunk, funnel-shifted into place,
+         * as long as those words lie inside the batch */
+        const uintptr_t a = reinterpret_cast<uintptr_t>(src);
+        const uint32_t* q = reinterpret_cast<const uint32_t*>(a & ~(uintptr_t)3);
+        const uint8_t* end = input + (size_t)gridDim.y * d.W * d.H;
+        if (reinterpret_cast<const uint8_t*>(q) >= input && reinterpret_cast<const uint8_t*>(q + 5) <= end) {
+            const uint32_t sh = (uint32_t)(a & 3) * 8;
+            const uint32_t w0 = __ldg(q), w1 = __ldg(q + 1), w2 = __ldg(q + 2), w3 = __ldg(q + 3), w4 = __ldg(q + 4);
+            *reinterpret_cast<uint4*>(dst) = make_uint4(__funnelshift_r(w0, w1, sh), __funnelshift_r(w1, w2, sh), __funnelshift_r(w2, w3, sh), __funnelshift_r(w3, w4, sh));
+            return;
+        }
+    }
+    for (int k = 0; k < 16 && px0 + k < L.w; k++) dst[k] = __ldg(src + k);
 }
 
 /* Levels >= 1: cv::resize(INTER_LINEAR) from the level below + copyMakeBorder in one pass

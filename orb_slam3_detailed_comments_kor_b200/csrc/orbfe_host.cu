@@ -156,7 +156,7 @@ int orbfe_extractor_create(const orbfe_params* p, int device, int width, int hei
     ex->maxBatch = max_batch;
     ex->lastBatch = 0;
     ex->params = *p;
-    ex->stream = nullptr; ex->copyIn = nullptr; ex->copyOut = nullptr; ex->side = nullptr; ex->evFork = nullptr; ex->evJoin = nullptr; ex->forkBlur = 1;
+    ex->stream = nullptr; ex->copyIn = nullptr; ex->copyOut = nullptr; ex->side = nullptr; ex->evFork = nullptr; ex->evJoin = nullptr; ex->forkBlur = 1; ex->fishLR = ex->fishRL = nullptr; ex->fishP3d = nullptr;
     ex->hKps = nullptr; ex->hDesc = nullptr; ex->hCount = nullptr; ex->hMono = nullptr;
     ex->profiling = 0; ex->stagePending = 0; ex->stereoPending = 0; ex->launches = 0; ex->batchFrames = 0; ex->bordersValid = 0;
     ex->graphExec = nullptr; ex->graphLap0 = ex->graphLap1 = 0; ex->graphLaunches = 0; ex->singleGraph = 1;
@@ -658,10 +658,23 @@ int orbfe_extract_batch_host(orbfe_extractor* ex, const uint8_t* h_images, int n
 /* One batch of stereo pairs through upload -> both extractions -> stereo matching -> download, enqueued chunk by chunk and not
  * waited for.  `slot` (0/1) selects the input staging buffers and the pinned count arrays, so that the upload of one batch can
  * run while the previous batch is still in the kernels. */
+struct FishArgs {   /* the fisheye-rig variant of the batch: ComputeStereoFishEyeMatches instead of ComputeStereoMatches */
+    const orbfe_fisheye_rig* rig;
+    double ratio;
+    int32_t *lr, *rl;   /* host outputs [nframes][cap] (may be NULL) */
+    float* p3d;         /* host output [nframes][cap][3] (may be NULL) */
+};
+
 static int stereo_frames_enqueue(orbfe_extractor* exL, orbfe_extractor* exR, const uint8_t* h_left, const uint8_t* h_right, int nframes, int lap0, int lap1,
                                  float mbf, float min_d, float max_d, orbfe_keypoint* kps_l, uint8_t* desc_l, orbfe_keypoint* kps_r, uint8_t* desc_r, int cap,
-                                 float* u_right, float* depth, int slot, int chunk) {
+                                 float* u_right, float* depth, int slot, int chunk, const FishArgs* fish) {
     const int kc = exL->d.kpCap;
+    if (fish && !exL->fishLR) {
+        const size_t n = (size_t)exL->maxBatch * kc;
+        ORBFE_CUDA(cudaMalloc((void**)&exL->fishLR, n * sizeof(int32_t))); exL->allocs.push_back(exL->fishLR);
+        ORBFE_CUDA(cudaMalloc((void**)&exL->fishRL, n * sizeof(int32_t))); exL->allocs.push_back(exL->fishRL);
+        ORBFE_CUDA(cudaMalloc((void**)&exL->fishP3d, n * 3 * sizeof(float))); exL->allocs.push_back(exL->fishP3d);
+    }
     const size_t frameBytes = (size_t)exL->d.W * exL->d.H;
     exL->lastBatch = exR->lastBatch = nframes;
     cudaStream_t sl = exL->stream, sr = exR->stream, in = exL->copyIn, out = exL->copyOut;
@@ -695,7 +708,9 @@ static int stereo_frames_enqueue(orbfe_extractor* exL, orbfe_extractor* exR, con
         if (rc) return rc;
         ORBFE_CUDA(cudaEventRecord(exR->evDone[k], sr));
         ORBFE_CUDA(cudaStreamWaitEvent(sl, exR->evDone[k], 0));
-        rc = orbfe_launch_stereo(exL, exR, nf, f0, mbf, min_d, max_d, sl);
+        if (fish) rc = orbfe_launch_fisheye(exL, exR, nf, f0, fish->ratio, fish->rig, exL->fishLR + (size_t)f0 * kc, exL->fishRL + (size_t)f0 * kc,
+                                            exL->b.depth + (size_t)f0 * kc, exL->fishP3d + (size_t)f0 * kc * 3, sl);
+        else rc = orbfe_launch_stereo(exL, exR, nf, f0, mbf, min_d, max_d, sl);
         if (rc) return rc;
         ORBFE_CUDA(cudaEventRecord(exL->evDone[k], sl));
         ORBFE_CUDA(cudaStreamWaitEvent(out, exL->evDone[k], 0));
@@ -714,6 +729,11 @@ static int stereo_frames_enqueue(orbfe_extractor* exL, orbfe_extractor* exR, con
         const size_t w = (size_t)kc * sizeof(float);
         if (u_right) ORBFE_CUDA(cudaMemcpy2DAsync(u_right + (size_t)f0 * cap, (size_t)cap * sizeof(float), exL->b.uRight + (size_t)f0 * kc, w, w, nf, cudaMemcpyDeviceToHost, out));
         if (depth) ORBFE_CUDA(cudaMemcpy2DAsync(depth + (size_t)f0 * cap, (size_t)cap * sizeof(float), exL->b.depth + (size_t)f0 * kc, w, w, nf, cudaMemcpyDeviceToHost, out));
+        if (fish) {
+            if (fish->lr) ORBFE_CUDA(cudaMemcpy2DAsync(fish->lr + (size_t)f0 * cap, (size_t)cap * 4, exL->fishLR + (size_t)f0 * kc, w, w, nf, cudaMemcpyDeviceToHost, out));
+            if (fish->rl) ORBFE_CUDA(cudaMemcpy2DAsync(fish->rl + (size_t)f0 * cap, (size_t)cap * 4, exL->fishRL + (size_t)f0 * kc, w, w, nf, cudaMemcpyDeviceToHost, out));
+            if (fish->p3d) ORBFE_CUDA(cudaMemcpy2DAsync(fish->p3d + (size_t)f0 * cap * 3, (size_t)cap * 12, exL->fishP3d + (size_t)f0 * kc * 3, 3 * w, 3 * w, nf, cudaMemcpyDeviceToHost, out));
+        }
         ORBFE_CUDA(cudaEventRecord(exL->evOut[k], out));
         exL->evOutValid[k] = 1;
     }
@@ -732,13 +752,13 @@ static int stereo_frames_check(orbfe_extractor* exL, orbfe_extractor* exR, const
 
 static int stereo_frames_submit(orbfe_extractor* exL, orbfe_extractor* exR, const uint8_t* h_left, const uint8_t* h_right, int nframes, int lap0, int lap1,
                                 float mbf, float min_d, float max_d, orbfe_keypoint* kps_l, uint8_t* desc_l, orbfe_keypoint* kps_r, uint8_t* desc_r, int cap,
-                                float* u_right, float* depth, int chunk) {
+                                float* u_right, float* depth, int chunk, const FishArgs* fish = nullptr) {
     int rc = stereo_frames_check(exL, exR, h_left, h_right, nframes, cap);
     if (rc) return rc;
     if (exL->pendingCount >= 2) { orbfe_set_error("two batches are already in flight: call orbfe_stereo_frames_wait first"); return ORBFE_E_CAPACITY; }
     ORBFE_CUDA(cudaSetDevice(exL->device));
     const int slot = (exL->pendingHead + exL->pendingCount) & 1;
-    rc = stereo_frames_enqueue(exL, exR, h_left, h_right, nframes, lap0, lap1, mbf, min_d, max_d, kps_l, desc_l, kps_r, desc_r, cap, u_right, depth, slot, chunk);
+    rc = stereo_frames_enqueue(exL, exR, h_left, h_right, nframes, lap0, lap1, mbf, min_d, max_d, kps_l, desc_l, kps_r, desc_r, cap, u_right, depth, slot, chunk, fish);
     if (rc) return rc;
     exL->pendingFrames[slot] = nframes;
     exL->pendingCount++;
@@ -752,6 +772,18 @@ int orbfe_stereo_frames_submit(orbfe_extractor* exL, orbfe_extractor* exR, const
      * large as in the synchronous call (fewer, fuller launches): measured 125.8 k -> 128.4 k frames/s on 256 EuRoC pairs */
     return stereo_frames_submit(exL, exR, h_left, h_right, nframes, lap0, lap1, mbf, min_d, max_d, kps_l, desc_l, kps_r, desc_r, cap, u_right, depth,
                                 exL ? 2 * exL->hostChunk : 0);
+}
+
+/* Frame's fisheye-rig constructor (src/Frame.cc:1023-1101) for a batch of pairs from host memory, pipelined like
+ * orbfe_stereo_frames_submit: both extractions with the lapping interval, then ComputeStereoFishEyeMatches (knn-2 + ratio,
+ * TriangulateMatches, the four output vectors).  Collected by orbfe_stereo_frames_wait. */
+int orbfe_fisheye_frames_submit(orbfe_extractor* exL, orbfe_extractor* exR, const uint8_t* h_left, const uint8_t* h_right, int nframes, int lap0, int lap1,
+                                const orbfe_fisheye_rig* rig, double ratio, orbfe_keypoint* kps_l, uint8_t* desc_l, orbfe_keypoint* kps_r, uint8_t* desc_r, int cap,
+                                int32_t* match_lr, int32_t* match_rl, float* depth, float* p3d) {
+    if (!rig) { orbfe_set_error("null rig"); return ORBFE_E_INVALID; }
+    const FishArgs fish = {rig, ratio, match_lr, match_rl, p3d};
+    return stereo_frames_submit(exL, exR, h_left, h_right, nframes, lap0, lap1, 0.f, 0.f, 0.f, kps_l, desc_l, kps_r, desc_r, cap, nullptr, depth,
+                                exL ? 2 * exL->hostChunk : 0, &fish);
 }
 
 int orbfe_stereo_frames_wait(orbfe_extractor* exL, orbfe_extractor* exR, int32_t* n_l, int32_t* mono_l, int32_t* n_r, int32_t* mono_r) {

@@ -129,6 +129,8 @@ struct orbfe_extractor {
     cudaStream_t side;                     /* the blur runs here, beside quadtree + assemble (they only meet again in k_orient_describe) */
     cudaEvent_t evFork, evJoin;
     int forkBlur;                          /* 0 with ORBFE_NO_FORK=1 */
+    int32_t *fishLR, *fishRL;              /* fisheye host pipeline: mvLeftToRightMatch / mvRightToLeftMatch per frame, allocated on first use */
+    float* fishP3d;                        /* mvStereo3Dpoints */
     std::vector<cudaEvent_t> evIn, evDone; /* one pair per chunk of hostChunk frames */
     std::vector<cudaEvent_t> evOut;        /* per chunk: the download of its results has finished (next batch may rewrite them) */
     std::vector<char> evOutValid;
@@ -163,6 +165,8 @@ struct orbfe_extractor {
 /* views of the per-frame buffers that start at frame f0 (kernels index frames from blockIdx) */
 ExBuffers orbfe_shift_frames(const ExBuffers& b, const ExDesc& d, int f0);
 /* Frame::ComputeStereoMatches kernels for frames [frame0, frame0 + nframes) of two extractors, enqueued on st */
+int orbfe_launch_fisheye(orbfe_extractor* exL, orbfe_extractor* exR, int nframes, int frame0, double ratio, const orbfe_fisheye_rig* rig, int32_t* lr, int32_t* rl,
+                         float* depth, float* p3d, cudaStream_t st);
 int orbfe_launch_stereo(orbfe_extractor* exL, orbfe_extractor* exR, int nframes, int frame0, float mbf, float minD, float maxD, cudaStream_t st);
 
 /* Getters wait for the object's own last work (not for the whole device: Tracking, LocalMapping and LoopClosing share the GPU)

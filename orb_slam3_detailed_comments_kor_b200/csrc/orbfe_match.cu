@@ -530,6 +530,23 @@ int orbfe_launch_stereo(orbfe_extractor* exL, orbfe_extractor* exR, int nframes,
     return ORBFE_OK;
 }
 
+/* knn-2 + ratio, then TriangulateMatches and the output vectors, for frames frame0 .. frame0+nframes-1 of the two objects; the four
+ * output pointers are those of the launch's first frame ([nframes][kpCap] each, p3d [nframes][kpCap][3]). */
+int orbfe_launch_fisheye(orbfe_extractor* exL, orbfe_extractor* exR, int nframes, int frame0, double ratio, const orbfe_fisheye_rig* rig, int32_t* lr, int32_t* rl,
+                         float* depth, float* p3d, cudaStream_t st) {
+    const ExBuffers bl = frame0 ? orbfe_shift_frames(exL->b, exL->d, frame0) : exL->b;
+    const ExBuffers br = frame0 ? orbfe_shift_frames(exR->b, exR->d, frame0) : exR->b;
+    FisheyeRig r;
+    static_assert(sizeof(FisheyeRig) == sizeof(orbfe_fisheye_rig), "rig layout");
+    memcpy(&r, rig, sizeof r);
+    k_fisheye_knn2<<<dim3((exL->d.kpCap + KB_NT - 1) / KB_NT, nframes), KB_NT, 0, st>>>(exL->d, bl, br, ratio, lr, nullptr);
+    ORBFE_CUDA(cudaMemsetAsync(rl, 0xFF, (size_t)nframes * exL->d.kpCap * sizeof(int32_t), st));
+    k_fisheye_triangulate<<<dim3((exL->d.kpCap + TR_NT - 1) / TR_NT, nframes), TR_NT, 0, st>>>(exL->d, bl, br, r, lr, rl, depth, p3d);
+    exL->launches += 2;
+    ORBFE_CUDA(cudaGetLastError());
+    return ORBFE_OK;
+}
+
 extern "C" {
 
 int orbfe_stereo_match_batch_device(orbfe_extractor* exL, orbfe_extractor* exR, int nframes, float mbf, float minD, float maxD, void* stream) {

@@ -136,6 +136,21 @@ def stereo_frames_submit(exL, exR, left, right, mbf, minD, maxD, vLappingArea, o
                                                 C.c_float(mbf), C.c_float(minD), C.c_float(maxD), ptr(kl), ptr(dl), ptr(kr), ptr(dr), cap, ptr(u), ptr(d)))
 
 
+def fisheye_frames_submit(exL, exR, left, right, rig, ratio, vLappingArea, out):
+    """orbfe_fisheye_frames_submit: like stereo_frames_submit for a fisheye rig.  `out` = (cntL, monoL, kpsL, descL, cntR, monoR, kpsR,
+    descR, match_lr[n, cap] i32, match_rl[n, cap] i32, depth[n, cap] f32, p3d[n, cap, 3] f32); collect with fisheye_frames_wait."""
+    nf, cap = left.shape[0], exL.capacity
+    cl, ml, kl, dl, cr, mr, kr, dr, lr, rl, d, p3 = out
+    rig = np.ascontiguousarray(rig, np.float32)
+    check(_lib.lib().orbfe_fisheye_frames_submit(exL.handle, exR.handle, ptr(left), ptr(right), nf, int(vLappingArea[0]), int(vLappingArea[1]), ptr(rig),
+                                                 C.c_double(ratio), ptr(kl), ptr(dl), ptr(kr), ptr(dr), cap, ptr(lr), ptr(rl), ptr(d), ptr(p3)))
+
+
+def fisheye_frames_wait(exL, exR, out):
+    check(_lib.lib().orbfe_stereo_frames_wait(exL.handle, exR.handle, ptr(out[0]), ptr(out[1]), ptr(out[4]), ptr(out[5])))
+    return out
+
+
 def stereo_frames_wait(exL, exR, out):
     """orbfe_stereo_frames_wait: block until the oldest submitted batch is on the host; fills the count arrays of `out`."""
     cl, ml, kl, dl, cr, mr, kr, dr, u, d = out

@@ -149,3 +149,59 @@ def test_gpu_fisheye_stereo_frame_on_device():
         kept += int(ok.sum())
     assert kept > 10, kept
     exL.close(); exR.close()
+
+
+@pytest.mark.gpu
+def test_gpu_fisheye_frames_submit_wait_equals_the_device_calls():
+    """orbfe_fisheye_frames_submit / orbfe_stereo_frames_wait (host images in, everything of the rig constructor out, two batches in
+    flight, chunked) against the per-step device calls on the same pairs."""
+    import torch
+    from orb_slam3_detailed_comments_kor_b200 import ORBextractor, synth
+    from orb_slam3_detailed_comments_kor_b200 import matcher as M
+    from orb_slam3_detailed_comments_kor_b200._lib import KP_DTYPE
+    W, H, params, nb = 512, 512, (1500, 1.2, 8, 20, 7), 70                       # two chunks, one of them short
+    cam = np.array([190.0, 190.0, 256.0, 256.0, 0.0, 0.0, 0.0, 0.0], np.float32)
+    rig = M.make_fisheye_rig(cam, cam, np.eye(3, dtype=np.float32), np.array([0.1, 0.0, 0.0], np.float32))
+    exL = ORBextractor(*params, width=W, height=H, max_batch=nb)
+    exR = ORBextractor(*params, width=W, height=H, max_batch=nb)
+    cap = exL.capacity
+    batches, want = [], []
+    for bi in range(3):
+        pairs = [synth.stereo_pair(7000 + 100 * bi + i, W, H) for i in range(nb)]
+        Ls = torch.from_numpy(np.stack([p[0] for p in pairs])).pin_memory().numpy(); Rs = torch.from_numpy(np.stack([p[1] for p in pairs])).pin_memory().numpy()
+        batches.append((Ls, Rs))
+        cl, ml, kl, dl = [a.copy() for a in exL.extract_batch_host(Ls, (0, 511))]
+        cr, mr, kr, dr = [a.copy() for a in exR.extract_batch_host(Rs, (0, 511))]
+        d_lr = torch.empty((nb, cap), dtype=torch.int32, device="cuda"); d_rl = torch.empty((nb, cap), dtype=torch.int32, device="cuda")
+        d_depth, d_p3d = torch.empty((nb, cap), device="cuda"), torch.empty((nb, cap, 3), device="cuda")
+        M.fisheye_match_batch_device(exL, exR, nb, 0.7, d_lr.data_ptr())
+        M.fisheye_triangulate_batch_device(exL, exR, nb, cam, cam, np.eye(3, dtype=np.float32), np.array([0.1, 0.0, 0.0], np.float32),
+                                           d_lr.data_ptr(), d_rl.data_ptr(), d_depth.data_ptr(), d_p3d.data_ptr())
+        torch.cuda.synchronize()
+        want.append((cl, ml, kl, dl, cr, mr, kr, dr, d_lr.cpu().numpy(), d_rl.cpu().numpy(), d_depth.cpu().numpy(), d_p3d.cpu().numpy()))
+
+    def out_set():
+        side = lambda: (np.zeros(nb, np.int32), np.zeros(nb, np.int32), np.zeros((nb, cap), KP_DTYPE), np.zeros((nb, cap, 32), np.uint8))  # noqa: E731
+        return side() + side() + (np.zeros((nb, cap), np.int32), np.zeros((nb, cap), np.int32), np.zeros((nb, cap), np.float32), np.zeros((nb, cap, 3), np.float32))
+    outs = [out_set(), out_set()]
+    got = []
+    M.fisheye_frames_submit(exL, exR, batches[0][0], batches[0][1], rig, 0.7, (0, 511), outs[0])
+    for k in range(1, 3):
+        M.fisheye_frames_submit(exL, exR, batches[k][0], batches[k][1], rig, 0.7, (0, 511), outs[k & 1])
+        got.append([a.copy() for a in M.fisheye_frames_wait(exL, exR, outs[(k - 1) & 1])])
+    got.append([a.copy() for a in M.fisheye_frames_wait(exL, exR, outs[0])])
+    kept = 0
+    for bi in range(3):
+        g, w = got[bi], want[bi]
+        for j in (0, 1, 4, 5):
+            assert np.array_equal(g[j], w[j]), "batch %d counts" % bi
+        for f in range(nb):
+            nl, nr = w[0][f], w[4][f]
+            assert np.array_equal(g[2][f, :nl], w[2][f, :nl]) and np.array_equal(g[3][f, :nl], w[3][f, :nl])
+            assert np.array_equal(g[6][f, :nr], w[6][f, :nr]) and np.array_equal(g[7][f, :nr], w[7][f, :nr])
+            assert np.array_equal(g[8][f, :nl], w[8][f, :nl]) and np.array_equal(g[9][f, :nr], w[9][f, :nr]), "batch %d frame %d matches" % (bi, f)
+            ok = w[8][f, :nl] >= 0
+            assert np.array_equal(g[10][f, :nl][ok], w[10][f, :nl][ok]) and np.array_equal(g[11][f, :nl][ok], w[11][f, :nl][ok])
+            kept += int(ok.sum())
+    assert kept > 50
+    exL.close(); exR.close()
