@@ -81,6 +81,8 @@ void orc_resize_linear_u8(const uint8_t* src, int sw, int sh, int sstep, uint8_t
 void orc_gaussian7_u8(const uint8_t* src, int w, int h, int sstep, uint8_t* dst, int dstep);
 int orc_fast9_16(const uint8_t* roi, int w, int h, int step, int threshold, orc_keypoint* out, int cap);
 float orc_fast_atan2(float y, float x);
+/* cv::SVD::compute on a row-major 4x4 float matrix: singular values and vt (triangulate_oracle.cpp; bit-exact against cv2.SVDecomp 4.13) */
+void orc_svd4x4_vt(const float* A, float* w, float* vt);
 
 /* ORBmatcher::DescriptorDistance, src/ORBmatcher.cc:2591-2607 */
 int orc_descriptor_distance(const uint8_t* a, const uint8_t* b);

@@ -52,6 +52,15 @@ def lib(fma=False):
     L.ref_distinctive_descriptor.argtypes = [vp, C.c_int, vp]
     L.ref_search_for_initialization.argtypes = [vp, vp, C.c_int, vp, vp, C.c_int, vp, vp, C.c_int, C.c_float, C.c_int, vp]
     L.ref_search_for_initialization.restype = C.c_int
+    L.ref_kb8_project.argtypes = [vp, vp, C.c_int, vp]
+    L.ref_kb8_project.restype = None
+    L.ref_kb8_unproject.argtypes = [vp, vp, C.c_int, vp]
+    L.ref_kb8_unproject.restype = None
+    L.ref_kb8_triangulate_matches.argtypes = [vp] * 8 + [C.c_int, vp, vp]
+    L.ref_kb8_triangulate_matches.restype = None
+    L.ref_search_for_triangulation.argtypes = ([vp, vp, vp, vp, C.c_int, C.c_int, vp, vp, vp, C.c_int] * 2
+                                               + [vp, C.c_int, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, vp, vp])
+    L.ref_search_for_triangulation.restype = C.c_int
     L.ref_search_by_projection.argtypes = [vp, vp, C.c_int, C.c_int, vp, vp, vp, vp, vp, vp, C.c_int, C.c_int] + [vp] * 12 + [C.c_float, C.c_float, vp]
     _libs[fma] = L
     return L
@@ -179,6 +188,55 @@ def search_for_initialization(kps1, desc1, kps2, desc2, grid4, prev_matched, win
     nm = lib().ref_search_for_initialization(_ptr(kps1), _ptr(desc1), kps1.shape[0], _ptr(kps2), _ptr(desc2), kps2.shape[0], _ptr(g), _ptr(prev), int(window),
                                              float(nnratio), int(check_orientation), _ptr(m12))
     return m12[:kps1.shape[0]], prev, nm
+
+
+def kb8_project(cam, p3):
+    cam, p3 = np.ascontiguousarray(cam, np.float32), np.ascontiguousarray(p3, np.float32).reshape(-1, 3)
+    uv = np.zeros((p3.shape[0], 2), np.float32)
+    lib().ref_kb8_project(_ptr(cam), _ptr(p3), p3.shape[0], _ptr(uv))
+    return uv
+
+
+def kb8_unproject(cam, uv):
+    cam, uv = np.ascontiguousarray(cam, np.float32), np.ascontiguousarray(uv, np.float32).reshape(-1, 2)
+    ray = np.zeros((uv.shape[0], 3), np.float32)
+    lib().ref_kb8_unproject(_ptr(cam), _ptr(uv), uv.shape[0], _ptr(ray))
+    return ray
+
+
+def kb8_triangulate_matches(cam1, cam2, R12, t12, uv1, uv2, sigma1, sigma2):
+    """The reference's own KannalaBrandt8::TriangulateMatches for n keypoint pairs: (depth[n] = return value, p3d[n, 3])."""
+    f = lambda a: np.ascontiguousarray(a, np.float32)  # noqa: E731
+    cam1, cam2, R12, t12, uv1, uv2, sigma1, sigma2 = f(cam1), f(cam2), f(R12), f(t12), f(uv1), f(uv2), f(sigma1), f(sigma2)
+    n = uv1.shape[0]
+    depth, p3d = np.zeros(n, np.float32), np.zeros((n, 3), np.float32)
+    lib().ref_kb8_triangulate_matches(_ptr(cam1), _ptr(cam2), _ptr(R12), _ptr(t12), _ptr(uv1), _ptr(uv2), _ptr(sigma1), _ptr(sigma2), n, _ptr(depth), _ptr(p3d))
+    return depth, p3d
+
+
+def search_for_triangulation(desc_1, kps_1, u_right_1, has_mp_1, n_left_1, fv_1, desc_2, kps_2, u_right_2, has_mp_2, n_left_2, fv_2, cams, rig, poses,
+                             scale_factors, level_sigma2, only_stereo=False, coarse=False, check_orientation=True):
+    """The reference's own ORBmatcher::SearchForTriangulation on arrays (oracle/ref_shim.cpp::ref_search_for_triangulation explains them).
+    fv = (nodes, starts, feats) arrays.  Returns (vMatches12, nmatches, geometry): geometry = (F12[3, 3], ep[2]) for pinhole keyframes,
+    (R[4, 3, 3], t[4, 3]) for a rig: the inputs of the library's entry point, evaluated by the reference's expressions."""
+    c = lambda a, t: None if a is None else np.ascontiguousarray(a, t)  # noqa: E731
+    p = lambda a: _ptr(a) if a is not None else None  # noqa: E731
+    d1, d2, k1, k2 = c(desc_1, np.uint8), c(desc_2, np.uint8), c(kps_1, KP_DTYPE), c(kps_2, KP_DTYPE)
+    u1, u2, m1, m2 = c(u_right_1, np.float32), c(u_right_2, np.float32), c(has_mp_1, np.uint8), c(has_mp_2, np.uint8)
+    (n1, s1, f1), (n2, s2, f2) = [tuple(c(a, np.int32) for a in fv) for fv in (fv_1, fv_2)]
+    cams, poses = c(np.asarray(cams, np.float32).reshape(32), np.float32), c(np.asarray(poses, np.float32).reshape(-1), np.float32)
+    assert poses.shape[0] == (48 if rig else 24)
+    if not rig:
+        poses = np.concatenate([poses, np.zeros(24, np.float32)])
+    sf, ls = c(scale_factors, np.float32), c(level_sigma2, np.float32)
+    out = np.zeros(max(d1.shape[0], 1), np.int32)
+    geom = np.zeros(48, np.float32)
+    nm = lib().ref_search_for_triangulation(p(d1), p(k1), p(u1), p(m1), d1.shape[0], int(n_left_1), p(n1), p(s1), p(f1), len(n1),
+                                            p(d2), p(k2), p(u2), p(m2), d2.shape[0], int(n_left_2), p(n2), p(s2), p(f2), len(n2),
+                                            p(cams), int(bool(rig)), p(poses), p(sf), p(ls), len(sf), int(only_stereo), int(coarse), int(check_orientation),
+                                            p(out), p(geom))
+    geometry = (geom[:36].reshape(4, 3, 3).copy(), geom[36:48].reshape(4, 3).copy()) if rig else (geom[:9].reshape(3, 3).copy(), geom[9:11].copy())
+    return out[:d1.shape[0]], nm, geometry
 
 
 def distinctive_descriptor(desc, bad_kf=None):

@@ -27,6 +27,7 @@
 #include <tuple>
 
 #include "refstub/cvstub.hpp"
+#include "ref_camera.h" /* GeometricCamera, Pinhole, KannalaBrandt8: member bodies from the reference, compiled in ref_camera_shim.cpp */
 #include "FeatureVector.h" /* the reference's vendored DBoW2 (Thirdparty/DBoW2/DBoW2): the real FeatureVector type */
 #include "ORBextractor.h"  /* the reference's header: -I/root/reference/include */
 
@@ -156,13 +157,24 @@ float Frame::mfGridElementWidthInv, Frame::mfGridElementHeightInv, Frame::mnMinX
 
 class KeyFrame {
 public:
+    /* what SearchForTriangulation reads (include/KeyFrame.h): poses as cv::Mat, the cameras, per-keypoint stereo coordinate, level tables */
+    cv::Mat mRcw, mtcw, mOw, mRrw, mtrw;
+    cv::Mat GetCameraCenter() { return mOw.clone(); }
+    cv::Mat GetRotation() { return mRcw.clone(); }
+    cv::Mat GetTranslation() { return mtcw.clone(); }
+    cv::Mat GetRightRotation() { return mRrw.clone(); }
+    cv::Mat GetRightTranslation() { return mtrw.clone(); }
+    MapPoint* GetMapPoint(const size_t& idx) { return mvpMapPoints[idx]; }
+    GeometricCamera* mpCamera = nullptr;
+    std::vector<float> mvuRight, mvScaleFactors, mvLevelSigma2;
+    int N = 0;
     std::vector<MapPoint*> GetMapPointMatches() { return mvpMapPoints; }
     std::vector<MapPoint*> mvpMapPoints;
     DBoW2::FeatureVector mFeatVec;
     cv::Mat mDescriptors;
     int NLeft = -1;
     std::vector<cv::KeyPoint> mvKeys, mvKeysRight, mvKeysUn;
-    void* mpCamera2 = nullptr;
+    GeometricCamera* mpCamera2 = nullptr;
     bool mbBadKF = false;
     bool isBad() { return mbBadKF; }
 };
@@ -175,6 +187,7 @@ public:
     int SearchByBoW(KeyFrame* pKF1, KeyFrame* pKF2, std::vector<MapPoint*>& vpMatches12);
     int SearchByProjection(Frame& F, const std::vector<MapPoint*>& vpMapPoints, const float th = 3, const bool bFarPoints = false, const float thFarPoints = 50.0f);
     int SearchForInitialization(Frame& F1, Frame& F2, std::vector<cv::Point2f>& vbPrevMatched, std::vector<int>& vnMatches12, int windowSize = 10);
+    int SearchForTriangulation(KeyFrame* pKF1, KeyFrame* pKF2, cv::Mat F12, std::vector<std::pair<size_t, size_t>>& vMatchedPairs, const bool bOnlyStereo, const bool bCoarse = false);
     float RadiusByViewingCos(const float& viewCos);
     void ComputeThreeMaxima(std::vector<int>* histo, const int L, int& ind1, int& ind2, int& ind3);
     static const int TH_LOW;
@@ -194,6 +207,7 @@ const int ORBmatcher::HISTO_LENGTH = 30;   /* src/ORBmatcher.cc:38 */
 #include "_ref/MapPoint_ComputeDistinctiveDescriptors.inc"
 #include "_ref/ORBmatcher_SearchByProjection.inc"
 #include "_ref/ORBmatcher_SearchForInitialization.inc"
+#include "_ref/ORBmatcher_SearchForTriangulation.inc"
 
 /* protected members of the extractor, for the stage-level comparisons */
 struct Probe : ORBextractor {
@@ -438,6 +452,127 @@ int ref_search_for_initialization(const orc_keypoint* kps1, const uint8_t* desc1
     ORBmatcher matcher(nnratio, check_orientation != 0);
     const int nm = matcher.SearchForInitialization(F1, F2, prev, m12, window);
     for (int i = 0; i < n1; i++) { matches12[i] = m12[i]; prev_matched[2 * i] = prev[i].x; prev_matched[2 * i + 1] = prev[i].y; }
+    return nm;
+}
+
+namespace {
+cv::Mat mat_from(const float* v, int r, int c) {
+    cv::Mat m(r, c, CV_32F);
+    for (int i = 0; i < r * c; i++) m.at<float>(i / c, i % c) = v[i];
+    return m;
+}
+void mat_to(const cv::Mat& m, float* out) {
+    for (int i = 0; i < m.rows; i++)
+        for (int j = 0; j < m.cols; j++) out[i * m.cols + j] = m.at<float>(i, j);
+}
+}  // namespace
+
+/* KannalaBrandt8::TriangulateMatches (src/CameraModels/KannalaBrandt8.cpp:338-407) for n keypoint pairs: depth[i] = its return value,
+ * p3d[3i..] = p3D when it was set (0 otherwise).  cam1 / cam2: mvParameters (8 floats). */
+void ref_kb8_triangulate_matches(const float* cam1, const float* cam2, const float* R12, const float* t12, const float* uv1, const float* uv2,
+                                 const float* sigma1, const float* sigma2, int n, float* depth, float* p3d) {
+    using namespace ORB_SLAM3;
+    ArenaScope scope;
+    KannalaBrandt8 c1(std::vector<float>(cam1, cam1 + 8)), c2(std::vector<float>(cam2, cam2 + 8));
+    const cv::Mat R = mat_from(R12, 3, 3), t = mat_from(t12, 3, 1);
+    for (int i = 0; i < n; i++) {
+        cv::KeyPoint k1, k2;
+        k1.pt = cv::Point2f(uv1[2 * i], uv1[2 * i + 1]);
+        k2.pt = cv::Point2f(uv2[2 * i], uv2[2 * i + 1]);
+        cv::Mat p;
+        depth[i] = c1.TriangulateMatches(&c2, k1, k2, R, t, sigma1[i], sigma2[i], p);
+        for (int k = 0; k < 3; k++) p3d[3 * i + k] = p.empty() ? 0.f : p.at<float>(k);
+    }
+}
+
+/* KannalaBrandt8::project / unproject (src/CameraModels/KannalaBrandt8.cpp:25-41, 96-125) on n points */
+void ref_kb8_project(const float* cam, const float* p3, int n, float* uv) {
+    ORB_SLAM3::KannalaBrandt8 c(std::vector<float>(cam, cam + 8));
+    for (int i = 0; i < n; i++) { const cv::Point2f r = c.project(cv::Point3f(p3[3 * i], p3[3 * i + 1], p3[3 * i + 2])); uv[2 * i] = r.x; uv[2 * i + 1] = r.y; }
+}
+void ref_kb8_unproject(const float* cam, const float* uv, int n, float* ray) {
+    ORB_SLAM3::KannalaBrandt8 c(std::vector<float>(cam, cam + 8));
+    for (int i = 0; i < n; i++) { const cv::Point3f r = c.unproject(cv::Point2f(uv[2 * i], uv[2 * i + 1])); ray[3 * i] = r.x; ray[3 * i + 1] = r.y; ray[3 * i + 2] = r.z; }
+}
+
+/* ORBmatcher::SearchForTriangulation (src/ORBmatcher.cc:965-1206) on two keyframes given as arrays.
+ *   kps / desc / has_mp [n]: keypoints (mvKeysUn, or mvKeys followed by mvKeysRight when n_left >= 0), descriptors, "has a map point";
+ *   u_right [n] or NULL (all -1); feature vector as (nodes [nfv], starts [nfv+1], feats);
+ *   cams [4][8]: keyframe 1 left, right, keyframe 2 left, right (a pinhole keyframe uses the first four numbers of its left entry);
+ *   rig != 0: both keyframes have a second camera (KannalaBrandt8), else both are Pinhole;
+ *   poses: Rcw[9], tcw[3] of keyframe 1, of keyframe 2, then (rig) Rrw[9], trw[3] = GetRightRotation / GetRightTranslation of 1 and of 2.
+ * geom_out: pinhole — F12[9] as Pinhole::epipolarConstrain forms it and the epipole ep[2] (:972-977); rig — R[4][9] then t[4][3] for the
+ * side pairs ll, lr, rl, rr (:995-1003): what the library's entry point takes as inputs, evaluated by the same expressions. */
+int ref_search_for_triangulation(const uint8_t* desc1, const orc_keypoint* kps1, const float* u_right1, const uint8_t* has_mp1, int n1, int n_left1,
+                                 const int32_t* nodes1, const int32_t* starts1, const int32_t* feats1, int nfv1, const uint8_t* desc2,
+                                 const orc_keypoint* kps2, const float* u_right2, const uint8_t* has_mp2, int n2, int n_left2, const int32_t* nodes2,
+                                 const int32_t* starts2, const int32_t* feats2, int nfv2, const float* cams, int rig, const float* poses,
+                                 const float* scale_factors, const float* level_sigma2, int nlevels, int only_stereo, int coarse, int check_orientation,
+                                 int32_t* match12, float* geom_out) {
+    using namespace ORB_SLAM3;
+    ArenaScope scope;
+    std::vector<GeometricCamera*> cam(4, nullptr);
+    for (int c = 0; c < 4; c++) {
+        if (rig) cam[c] = new KannalaBrandt8(std::vector<float>(cams + 8 * c, cams + 8 * c + 8));
+        else if (c % 2 == 0) cam[c] = new Pinhole(std::vector<float>(cams + 8 * c, cams + 8 * c + 4));
+    }
+    MapPoint some;
+    auto fill = [&](KeyFrame& kf, const uint8_t* desc, const orc_keypoint* kps, const float* ur, const uint8_t* has, int n, int nl, const int32_t* nodes,
+                    const int32_t* starts, const int32_t* feats, int nfv, const float* pose, const float* poseR, GeometricCamera* cl, GeometricCamera* cr) {
+        kf.N = n; kf.NLeft = rig ? nl : -1;
+        kf.mDescriptors = cv::Mat(n, 32, CV_8UC1, (void*)desc, 32);
+        std::vector<cv::KeyPoint> all(n);
+        if (n) std::memcpy((void*)all.data(), kps, sizeof(orc_keypoint) * n);
+        if (!rig) kf.mvKeysUn = kf.mvKeys = all;
+        else { kf.mvKeys.assign(all.begin(), all.begin() + nl); kf.mvKeysRight.assign(all.begin() + nl, all.end()); }
+        kf.mvuRight.assign(n, -1.f);
+        if (ur) kf.mvuRight.assign(ur, ur + n);
+        kf.mvpMapPoints.assign(n, nullptr);
+        for (int i = 0; i < n; i++) if (has && has[i]) kf.mvpMapPoints[i] = &some;
+        for (int k = 0; k < nfv; k++)
+            for (int j = starts[k]; j < starts[k + 1]; j++) kf.mFeatVec.addFeature((DBoW2::NodeId)nodes[k], (unsigned)feats[j]);
+        kf.mvScaleFactors.assign(scale_factors, scale_factors + nlevels);
+        kf.mvLevelSigma2.assign(level_sigma2, level_sigma2 + nlevels);
+        kf.mRcw = mat_from(pose, 3, 3); kf.mtcw = mat_from(pose + 9, 3, 1);
+        kf.mOw = -kf.mRcw.t() * kf.mtcw;                                    /* KeyFrame::SetPose: Ow = -Rwc * tcw */
+        if (rig) { kf.mRrw = mat_from(poseR, 3, 3); kf.mtrw = mat_from(poseR + 9, 3, 1); }
+        kf.mpCamera = cl; kf.mpCamera2 = rig ? cr : nullptr;
+    };
+    KeyFrame kf1, kf2;
+    fill(kf1, desc1, kps1, u_right1, has_mp1, n1, n_left1, nodes1, starts1, feats1, nfv1, poses, poses + 24, cam[0], cam[1]);
+    fill(kf2, desc2, kps2, u_right2, has_mp2, n2, n_left2, nodes2, starts2, feats2, nfv2, poses + 12, poses + 36, cam[2], cam[3]);
+    ORBmatcher matcher(0.6f, check_orientation != 0);
+    std::vector<std::pair<size_t, size_t>> pairs;
+    const int nm = matcher.SearchForTriangulation(&kf1, &kf2, cv::Mat(), pairs, only_stereo != 0, coarse != 0);
+    for (int i = 0; i < n1; i++) match12[i] = -1;
+    for (const auto& pr : pairs) match12[pr.first] = (int32_t)pr.second;
+    if (geom_out) {
+        if (!rig) {   /* the same expressions as :972-977, :990-993 and Pinhole.cpp:137-140 */
+            cv::Mat Cw = kf1.GetCameraCenter(), R2w = kf2.GetRotation(), t2w = kf2.GetTranslation();
+            cv::Mat C2 = R2w * Cw + t2w;
+            const cv::Point2f ep = kf2.mpCamera->project(C2);
+            cv::Mat R1w = kf1.GetRotation(), t1w = kf1.GetTranslation();
+            cv::Mat R12 = R1w * R2w.t();
+            cv::Mat t12 = -R1w * R2w.t() * t2w + t1w;
+            Pinhole* p1 = static_cast<Pinhole*>(kf1.mpCamera);
+            cv::Mat t12x = p1->SkewSymmetricMatrix(t12);
+            cv::Mat K1 = p1->toK(), K2 = kf2.mpCamera->toK();
+            cv::Mat F12 = K1.t().inv() * t12x * R12 * K2.inv();
+            mat_to(F12, geom_out);
+            geom_out[9] = ep.x; geom_out[10] = ep.y;
+        } else {
+            cv::Mat R[4], t[4];
+            R[0] = kf1.GetRotation() * kf2.GetRotation().t();
+            R[1] = kf1.GetRotation() * kf2.GetRightRotation().t();
+            R[2] = kf1.GetRightRotation() * kf2.GetRotation().t();
+            R[3] = kf1.GetRightRotation() * kf2.GetRightRotation().t();
+            t[0] = kf1.GetRotation() * (-kf2.GetRotation().t() * kf2.GetTranslation()) + kf1.GetTranslation();
+            t[1] = kf1.GetRotation() * (-kf2.GetRightRotation().t() * kf2.GetRightTranslation()) + kf1.GetTranslation();
+            t[2] = kf1.GetRightRotation() * (-kf2.GetRotation().t() * kf2.GetTranslation()) + kf1.GetRightTranslation();
+            t[3] = kf1.GetRightRotation() * (-kf2.GetRightRotation().t() * kf2.GetRightTranslation()) + kf1.GetRightTranslation();
+            for (int c = 0; c < 4; c++) { mat_to(R[c], geom_out + 9 * c); mat_to(t[c], geom_out + 36 + 3 * c); }
+        }
+    }
     return nm;
 }
 

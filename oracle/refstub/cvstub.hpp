@@ -35,7 +35,8 @@ typedef unsigned char uchar;
 #define CV_PI 3.1415926535897932384626433832795
 #define CV_8U 0
 #define CV_8UC1 0
-#define CV_32F 5   /* only FORB::toMat32F (Thirdparty/DBoW2/DBoW2/FORB.cpp:138-170, unused here) asks for it */
+#define CV_32F 5   /* the small float matrices of the matcher and camera-model bodies (cvstub_float.hpp); the pixel routines are 8-bit only */
+#define CV_32FC1 5
 
 /* cvRound = round half to even in the current (default) rounding mode, like OpenCV's SSE2 / lrint paths. */
 static inline int cvRound(double v) { return (int)std::lrint(v); }
@@ -88,6 +89,7 @@ enum { INTER_LINEAR = 1 };
 enum { NORM_L1 = 2 };
 
 class _OutputArray;
+struct MatExpr;
 
 /* 8-bit single-channel matrix header over a shared buffer.  `origin`/`wholeRows`/`wholeCols` describe the
  * allocation a view was cut from (what Mat::locateROI reports), which copyMakeBorder without BORDER_ISOLATED needs. */
@@ -106,15 +108,17 @@ public:
     Mat(int r, int c, int type) { alloc(r, c, type); }
     /* header over caller memory (used by the C entry points of ref_shim.cpp, not by the reference) */
     Mat(int r, int c, int type, void* ext, size_t extStep)
-        : rows(r), cols(c), data((uchar*)ext), step{extStep}, origin((uchar*)ext), wholeRows(r), wholeCols(c), type_(type) { assert(type == CV_8UC1); }
+        : rows(r), cols(c), data((uchar*)ext), step{extStep}, origin((uchar*)ext), wholeRows(r), wholeCols(c), type_(type) { assert(type == CV_8UC1 || type == CV_32F); }
 
     static Mat zeros(int r, int c, int type) {
         Mat m(r, c, type);
-        if (m.data) std::memset(m.data, 0, (size_t)r * c);
+        if (m.data) std::memset(m.data, 0, (size_t)r * c * m.elemSize());
         return m;
     }
 
     int type() const { return type_; }
+    size_t elemSize() const { return type_ == CV_32F ? 4 : 1; }
+    size_t total() const { return (size_t)rows * cols; }
     bool empty() const { return data == nullptr || rows == 0 || cols == 0; }
     size_t step1() const { return step.v; }
 
@@ -124,14 +128,25 @@ public:
     Mat row(int y) const { return view(y, y + 1, 0, cols); }
 
     Mat clone() const {
-        Mat m(rows, cols, CV_8UC1);
-        for (int y = 0; y < rows; ++y) std::memcpy(m.data + (size_t)y * m.step.v, data + (size_t)y * step.v, cols);
+        Mat m(rows, cols, type_);
+        for (int y = 0; y < rows; ++y) std::memcpy(m.data + (size_t)y * m.step.v, data + (size_t)y * step.v, cols * elemSize());
         return m;
     }
     inline void copyTo(const _OutputArray& dst) const;
 
-    template <typename T> T& at(int y, int x) { static_assert(sizeof(T) == 1, "8-bit only"); return *(T*)(data + (size_t)y * step.v + x); }
-    template <typename T> const T& at(int y, int x) const { static_assert(sizeof(T) == 1, "8-bit only"); return *(const T*)(data + (size_t)y * step.v + x); }
+    template <typename T> T& at(int y, int x) { assert(sizeof(T) == elemSize()); return *(T*)(data + (size_t)y * step.v + (size_t)x * sizeof(T)); }
+    template <typename T> const T& at(int y, int x) const { assert(sizeof(T) == elemSize()); return *(const T*)(data + (size_t)y * step.v + (size_t)x * sizeof(T)); }
+    /* element i of a row or column vector */
+    template <typename T> T& at(int i) { return rows == 1 ? at<T>(0, i) : at<T>(i, 0); }
+    template <typename T> const T& at(int i) const { return rows == 1 ? at<T>(0, i) : at<T>(i, 0); }
+    Mat col(int x) const { return view(0, rows, x, x + 1); }
+    inline Mat t() const;
+    inline Mat inv() const;
+    inline double dot(const Mat& b) const;
+    inline Mat& operator=(const MatExpr& e);
+    Mat(const Mat&) = default;
+    Mat& operator=(const Mat&) = default;
+    inline Mat(const MatExpr& e);
     uchar* ptr(int y = 0) { return data + (size_t)y * step.v; }
     const uchar* ptr(int y = 0) const { return data + (size_t)y * step.v; }
     template <typename T> T* ptr(int y = 0) { return (T*)(data + (size_t)y * step.v); }
@@ -157,7 +172,7 @@ public:
     void locateROI(Size& whole, Point& ofs) const {
         whole = Size(wholeCols, wholeRows);
         size_t d = (size_t)(data - origin);
-        ofs = Point((int)(d % step.v), (int)(d / step.v));
+        ofs = Point((int)(d % step.v / elemSize()), (int)(d / step.v));
     }
 
 private:
@@ -179,7 +194,7 @@ private:
         assert(0 <= y0 && y0 <= y1 && y1 <= rows && 0 <= x0 && x0 <= x1 && x1 <= cols);
         Mat m(*this);
         m.rows = y1 - y0; m.cols = x1 - x0;
-        m.data = data + (size_t)y0 * step.v + x0;
+        m.data = data + (size_t)y0 * step.v + (size_t)x0 * elemSize();
         return m;
     }
 };
@@ -341,5 +356,7 @@ public:
 template <typename T> inline FileStorage& operator<<(FileStorage& fs, const T&) { std::abort(); return fs; }
 
 }  // namespace cv
+
+#include "cvstub_float.hpp"
 
 #endif

@@ -132,8 +132,10 @@ void kb8_project(const Kb8& c, const float p[3], float uv[2]) {
     const float psi = atan2f(p[1], p[0]);
     const float t2 = theta * theta, t3 = theta * t2, t5 = t3 * t2, t7 = t5 * t2, t9 = t7 * t2;
     const float r = theta + c.k0 * t3 + c.k1 * t5 + c.k2 * t7 + c.k3 * t9;
-    uv[0] = c.fx * r * cosf(psi) + c.cx;
-    uv[1] = c.fy * r * sinf(psi) + c.cy;
+    /* `cos(psi)` / `sin(psi)` on a float, with no std overloads in scope in the reference's translation unit, are ::cos(double) / ::sin(double):
+     * product and sum in double, one rounding in cv::Point2f's constructor (oracle/ref_camera_shim.cpp asserts the overload that is taken) */
+    uv[0] = (float)((double)(c.fx * r) * cos((double)psi) + (double)c.cx);
+    uv[1] = (float)((double)(c.fy * r) * sin((double)psi) + (double)c.cy);
 }
 
 /* Mat::dot / cv::norm on 3-vectors: products summed in double */

@@ -529,6 +529,7 @@ static int pair_batch_device(orbfe_extractor* exL, orbfe_extractor* exR, const u
         orbfe_set_error("nframes %d outside [1, max_batch=%d]", nframes, exL->maxBatch < exR->maxBatch ? exL->maxBatch : exR->maxBatch);
         return ORBFE_E_CAPACITY;
     }
+    if (exL->pendingCount) { orbfe_set_error("batches submitted with orbfe_stereo_frames_submit are still in flight"); return ORBFE_E_INVALID; }
     ORBFE_CUDA(cudaSetDevice(exL->device));
     cudaStream_t sl = exL->stream, sr = exR->stream;
     if (user) {

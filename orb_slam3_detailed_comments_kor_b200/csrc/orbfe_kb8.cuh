@@ -35,8 +35,12 @@ static __device__ void kb8_project(const Kb8Cam& c, const float (&p)[3], float (
     const float psi = atan2f(p[1], p[0]);
     const float t2 = theta * theta, t3 = theta * t2, t5 = t3 * t2, t7 = t5 * t2, t9 = t7 * t2;
     const float r = theta + c.k0 * t3 + c.k1 * t5 + c.k2 * t7 + c.k3 * t9;
-    uv[0] = c.fx * r * cosf(psi) + c.cx;
-    uv[1] = c.fy * r * sinf(psi) + c.cy;
+    /* the reference writes `cos(psi)` / `sin(psi)` on a float with no std overloads in scope (:39-40): the C library's double functions,
+     * so the product and the sum are evaluated in double and rounded once by cv::Point2f's constructor */
+    double sn, cs;
+    sincos((double)psi, &sn, &cs);
+    uv[0] = (float)((double)(c.fx * r) * cs + (double)c.cx);
+    uv[1] = (float)((double)(c.fy * r) * sn + (double)c.cy);
 }
 
 static __device__ __forceinline__ double dot3d(const float* a, const float* b) { return (double)a[0] * b[0] + (double)a[1] * b[1] + (double)a[2] * b[2]; }
