@@ -52,6 +52,9 @@ def lib(fma=False):
     L.ref_distinctive_descriptor.argtypes = [vp, C.c_int, vp]
     L.ref_search_for_initialization.argtypes = [vp, vp, C.c_int, vp, vp, C.c_int, vp, vp, C.c_int, C.c_float, C.c_int, vp]
     L.ref_search_for_initialization.restype = C.c_int
+    L.ref_search_by_projection_last_frame.argtypes = [vp, vp, C.c_int, C.c_int, vp, vp, vp, vp, vp, C.c_int, C.c_float, C.c_float, vp, vp, vp, vp, C.c_int, C.c_int,
+                                                      vp, vp, vp, vp, vp, vp, C.c_float, C.c_int, C.c_int, vp]
+    L.ref_search_by_projection_last_frame.restype = C.c_int
     L.ref_kb8_project.argtypes = [vp, vp, C.c_int, vp]
     L.ref_kb8_project.restype = None
     L.ref_kb8_unproject.argtypes = [vp, vp, C.c_int, vp]
@@ -188,6 +191,23 @@ def search_for_initialization(kps1, desc1, kps2, desc2, grid4, prev_matched, win
     nm = lib().ref_search_for_initialization(_ptr(kps1), _ptr(desc1), kps1.shape[0], _ptr(kps2), _ptr(desc2), kps2.shape[0], _ptr(g), _ptr(prev), int(window),
                                              float(nnratio), int(check_orientation), _ptr(m12))
     return m12[:kps1.shape[0]], prev, nm
+
+
+def search_by_projection_last_frame(kps, desc, n_left, u_right, obs_cur, grid4, bounds4, scale_factors, mbf, mb, Tcw, Trl, cam4, kps_last, n_left_last, has_mp,
+                                    outlier, world, obs_mp, desc_mp, Tlw, th, mono, check_orientation):
+    """The reference's own ORBmatcher::SearchByProjection(CurrentFrame, LastFrame, th, bMono) on arrays (see ref_shim.cpp).
+    Returns (owner[n], nmatches)."""
+    c = lambda a, t: None if a is None else np.ascontiguousarray(a, t)  # noqa: E731
+    p = lambda a: _ptr(a) if a is not None else None  # noqa: E731
+    f = np.float32
+    kps, desc, ur, oc = c(kps, KP_DTYPE), c(desc, np.uint8), c(u_right, f), c(obs_cur, np.int32)
+    g, b, sf, Tcw, Trl, cam4 = c(grid4, f), c(bounds4, f), c(scale_factors, f), c(np.asarray(Tcw, f).reshape(16), f), c(np.asarray(Trl, f).reshape(12), f), c(cam4, f)
+    kl, hm, ol, w, om, dm, Tlw = c(kps_last, KP_DTYPE), c(has_mp, np.uint8), c(outlier, np.uint8), c(world, f), c(obs_mp, np.int32), c(desc_mp, np.uint8), c(np.asarray(Tlw, f).reshape(16), f)
+    owner = np.zeros(max(len(kps), 1), np.int32)
+    nm = lib().ref_search_by_projection_last_frame(p(kps), p(desc), len(kps), int(n_left), p(ur), p(oc), p(g), p(b), p(sf), len(sf), float(mbf), float(mb), p(Tcw), p(Trl),
+                                                   p(cam4), p(kl), len(kl), int(n_left_last), p(hm), p(ol), p(w), p(om), p(dm), p(Tlw), float(th), int(mono),
+                                                   int(check_orientation), p(owner))
+    return owner[:len(kps)], nm
 
 
 def kb8_project(cam, p3):

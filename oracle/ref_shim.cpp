@@ -124,6 +124,8 @@ public:
     cv::Mat mDescriptor;
     int Observations() { return nObs; }
     cv::Mat GetDescriptor() { return mDescriptor.clone(); }
+    cv::Mat mWorldPos;
+    cv::Mat GetWorldPos() { return mWorldPos.clone(); }
 };
 
 #define FRAME_GRID_ROWS 48 /* include/Frame.h:37-38 */
@@ -152,7 +154,13 @@ public:
     std::vector<std::size_t> mGridRight[FRAME_GRID_COLS][FRAME_GRID_ROWS];
     std::vector<MapPoint*> mvpMapPoints;
     std::vector<int> mvLeftToRightMatch, mvRightToLeftMatch;
+    /* what SearchByProjection(CurrentFrame, LastFrame, ...) reads on top (include/Frame.h) */
+    cv::Mat mTcw, mTrl;
+    std::vector<bool> mvbOutlier;
+    GeometricCamera* mpCamera = nullptr;
+    static float mnMaxX, mnMaxY;
 };
+float Frame::mnMaxX, Frame::mnMaxY;
 float Frame::mfGridElementWidthInv, Frame::mfGridElementHeightInv, Frame::mnMinX, Frame::mnMinY;
 
 class KeyFrame {
@@ -188,6 +196,7 @@ public:
     int SearchByProjection(Frame& F, const std::vector<MapPoint*>& vpMapPoints, const float th = 3, const bool bFarPoints = false, const float thFarPoints = 50.0f);
     int SearchForInitialization(Frame& F1, Frame& F2, std::vector<cv::Point2f>& vbPrevMatched, std::vector<int>& vnMatches12, int windowSize = 10);
     int SearchForTriangulation(KeyFrame* pKF1, KeyFrame* pKF2, cv::Mat F12, std::vector<std::pair<size_t, size_t>>& vMatchedPairs, const bool bOnlyStereo, const bool bCoarse = false);
+    int SearchByProjection(Frame& CurrentFrame, const Frame& LastFrame, const float th, const bool bMono);
     float RadiusByViewingCos(const float& viewCos);
     void ComputeThreeMaxima(std::vector<int>* histo, const int L, int& ind1, int& ind2, int& ind3);
     static const int TH_LOW;
@@ -208,6 +217,7 @@ const int ORBmatcher::HISTO_LENGTH = 30;   /* src/ORBmatcher.cc:38 */
 #include "_ref/ORBmatcher_SearchByProjection.inc"
 #include "_ref/ORBmatcher_SearchForInitialization.inc"
 #include "_ref/ORBmatcher_SearchForTriangulation.inc"
+#include "_ref/ORBmatcher_SearchByProjectionLastFrame.inc"
 
 /* protected members of the extractor, for the stage-level comparisons */
 struct Probe : ORBextractor {
@@ -483,6 +493,65 @@ void ref_kb8_triangulate_matches(const float* cam1, const float* cam2, const flo
         depth[i] = c1.TriangulateMatches(&c2, k1, k2, R, t, sigma1[i], sigma2[i], p);
         for (int k = 0; k < 3; k++) p3d[3 * i + k] = p.empty() ? 0.f : p.at<float>(k);
     }
+}
+
+/* ORBmatcher::SearchByProjection(CurrentFrame, LastFrame, th, bMono) (src/ORBmatcher.cc:2193-2419) on two frames given as arrays.
+ *   current frame: kps / desc [n] (rows >= n_left: the right camera; n_left = -1: one camera), u_right [n] or NULL, obs_cur [n] = -1 no map
+ *   point, else Observations() of the one the row holds; grid4 + bounds4 (mnMinX, mnMinY, inv widths; mnMinX, mnMaxX, mnMinY, mnMaxY); Tcw [16],
+ *   Trl [12] (3x4, rig only); cam: Pinhole fx, fy, cx, cy;
+ *   last frame: nl rows with octave / angle in kps_last (n_left_last like above), has_mp / outlier [nl], world [nl][3], obs_mp [nl], desc_mp
+ *   [nl][32], Tlw [16].
+ * owner[row] = index of the last-frame row whose map point the row holds afterwards, -2 = the initial one, -1 = none. */
+int ref_search_by_projection_last_frame(const orc_keypoint* kps, const uint8_t* desc, int n, int n_left, const float* u_right, const int32_t* obs_cur,
+                                        const float* grid4, const float* bounds4, const float* scale_factors, int nlevels, float mbf, float mb, const float* Tcw,
+                                        const float* Trl, const float* cam4, const orc_keypoint* kps_last, int nl, int n_left_last, const uint8_t* has_mp,
+                                        const uint8_t* outlier, const float* world, const int32_t* obs_mp, const uint8_t* desc_mp, const float* Tlw, float th,
+                                        int mono, int check_orientation, int32_t* owner) {
+    using namespace ORB_SLAM3;
+    ArenaScope scope;
+    Frame F, Last;
+    Frame::mnMinX = grid4[0]; Frame::mnMinY = grid4[1]; Frame::mfGridElementWidthInv = grid4[2]; Frame::mfGridElementHeightInv = grid4[3];
+    Frame::mnMaxX = bounds4[1]; Frame::mnMaxY = bounds4[3];
+    Pinhole camera(std::vector<float>(cam4, cam4 + 4));
+    F.N = n; F.Nleft = n_left; F.mbf = mbf; F.mb = mb; F.mpCamera = &camera;
+    F.mDescriptors = cv::Mat(n, 32, CV_8UC1, (void*)desc, 32);
+    std::vector<cv::KeyPoint> all(n);
+    if (n) std::memcpy((void*)all.data(), kps, sizeof(orc_keypoint) * n);
+    if (n_left < 0) F.mvKeysUn = F.mvKeys = all;
+    else { F.mvKeys.assign(all.begin(), all.begin() + n_left); F.mvKeysRight.assign(all.begin() + n_left, all.end()); }
+    F.mvuRight.assign(n, -1.f);
+    if (u_right) F.mvuRight.assign(u_right, u_right + n);
+    F.mvScaleFactors.assign(scale_factors, scale_factors + nlevels);
+    F.mTcw = mat_from(Tcw, 4, 4);
+    if (n_left >= 0) F.mTrl = mat_from(Trl, 3, 4);
+    F.AssignFeaturesToGrid();
+    std::vector<MapPoint> initial(n);
+    F.mvpMapPoints.assign(n, nullptr);
+    for (int i = 0; i < n; i++)
+        if (obs_cur[i] >= 0) { initial[i].nObs = obs_cur[i]; F.mvpMapPoints[i] = &initial[i]; }
+    Last.N = nl; Last.Nleft = n_left_last;
+    Last.mTcw = mat_from(Tlw, 4, 4);
+    std::vector<cv::KeyPoint> lall(nl);
+    if (nl) std::memcpy((void*)lall.data(), kps_last, sizeof(orc_keypoint) * nl);
+    if (n_left_last < 0) Last.mvKeysUn = Last.mvKeys = lall;
+    else { Last.mvKeys.assign(lall.begin(), lall.begin() + n_left_last); Last.mvKeysRight.assign(lall.begin() + n_left_last, lall.end()); }
+    std::vector<MapPoint> store(nl);
+    Last.mvpMapPoints.assign(nl, nullptr);
+    Last.mvbOutlier.assign(nl, false);
+    for (int i = 0; i < nl; i++) {
+        store[i].nObs = obs_mp[i];
+        store[i].mWorldPos = mat_from(world + 3 * i, 3, 1);
+        store[i].mDescriptor = cv::Mat(1, 32, CV_8UC1, (void*)(desc_mp + (size_t)i * 32), 32);
+        if (has_mp[i]) Last.mvpMapPoints[i] = &store[i];
+        Last.mvbOutlier[i] = outlier[i] != 0;
+    }
+    ORBmatcher matcher(0.9f, check_orientation != 0);
+    const int nm = matcher.SearchByProjection(F, Last, th, mono != 0);
+    for (int i = 0; i < n; i++) {
+        MapPoint* p = F.mvpMapPoints[i];
+        owner[i] = !p ? -1 : (p >= initial.data() && p < initial.data() + n) ? -2 : (int32_t)(p - store.data());
+    }
+    return nm;
 }
 
 /* KannalaBrandt8::project / unproject (src/CameraModels/KannalaBrandt8.cpp:25-41, 96-125) on n points */

@@ -366,3 +366,86 @@ def test_distinctive_descriptors_equal_reference():
     keep = np.nonzero(bad == 0)[0]
     sub_idx, _ = O.distinctive_descriptors(rows[keep], np.array([0, len(keep)], np.int32))
     assert keep[sub_idx[0]] == Rf.distinctive_descriptor(rows, bad)
+
+
+@pytest.mark.parametrize("motion,mono", [("still", False), ("forward", False), ("backward", False), ("forward", True)])
+@pytest.mark.parametrize("name,kw", [("pinhole", dict(seed=61, n=800, stereo_gate=True)), ("rig", dict(seed=62, n=900, fisheye=True)),
+                                     ("crowded", dict(seed=63, n=500))])
+def test_search_by_projection_last_frame_equals_reference(name, kw, motion, mono):
+    """ORBmatcher::SearchByProjection(CurrentFrame, LastFrame, th, bMono) (src/ORBmatcher.cc:2193-2419, Tracking::TrackWithMotionModel) — the
+    reference's own body, compiled (with the `;` its line 2226 lacks) — against the oracle driven through the query list INTEGRATION.md 5a
+    prescribes for this overload: ORBFE_PQ_BEST_ONLY queries, ORBFE_PQ_BLOCKS iff the map point has observations, the level window of the
+    motion, the right-camera half flagged ORBFE_PQ_NEEDS_LEFT_WINDOW, the rotation check on.  Every row of the current frame must end up
+    with the same map point and nmatches must agree.  The camera and pose are chosen so that the projection is exact (identity pose, unit
+    focal length, depth 1): what is compared is the search, not the projection arithmetic that stays with the caller."""
+    from orb_slam3_detailed_comments_kor_b200.synth import projection_cases as PC
+    f32 = np.float32
+    c = PC.make_case(nq=1, **kw)
+    kps, desc, grid = c["kps"], c["desc"], c["grid"]
+    n, n_left = len(kps), int(c["n_left"][0])
+    W, H = 752.0, 480.0
+    rng = np.random.RandomState(kw["seed"] + 1000)
+    scale = np.array([f32(1.2) ** i for i in range(8)], f32)
+    th = f32(7.0 if name != "crowded" else 15.0)
+    mbf, mb = f32(40.0), f32(0.1)
+    u_right = None
+    if n_left < 0 and name == "pinhole":
+        u_right = np.where(rng.uniform(size=n) < 0.6, kps["x"] - mbf + rng.uniform(-12, 12, n), -1).astype(f32)
+    obs_cur = np.where(rng.uniform(size=n) < 0.1, rng.randint(0, 2, n), -1).astype(np.int32)
+    nl = 700
+    kl = np.zeros(nl, PC.KP_DTYPE)
+    kl["octave"] = np.minimum(rng.geometric(0.35, nl) - 1, 7)
+    turn = rng.uniform(-40, 40)
+    hot = rng.choice(n, 12, replace=False)
+    tgt = np.where(rng.uniform(size=nl) < (0.6 if name == "crowded" else 0.15), hot[rng.randint(0, 12, nl)], rng.randint(0, n, nl))
+    radius = (th * scale[kl["octave"]]).astype(f32)
+    x = (kps["x"][tgt] + rng.uniform(-0.6, 0.6, nl) * radius).astype(f32)
+    y = (kps["y"][tgt] + rng.uniform(-0.6, 0.6, nl) * radius).astype(f32)
+    far = rng.uniform(size=nl) < 0.1
+    x[far] = rng.uniform(-40, W + 40, int(far.sum())).astype(f32); y[far] = rng.uniform(-40, H + 40, int(far.sum())).astype(f32)
+    kl["angle"] = np.where(rng.uniform(size=nl) < 0.8, kps["angle"][tgt] + turn + rng.uniform(-4, 4, nl), rng.uniform(0, 360, nl)).astype(f32) % f32(360)
+    z = np.where(rng.uniform(size=nl) < 0.05, -1.0, 1.0).astype(f32)
+    world = np.stack([x * z, y * z, z], 1).astype(f32)                    # identity pose, unit pinhole: the projection is (x, y) exactly
+    has_mp = (rng.uniform(size=nl) < 0.9).astype(np.uint8)
+    outlier = (rng.uniform(size=nl) < 0.05).astype(np.uint8)
+    obs_mp = np.where(rng.uniform(size=nl) < 0.2, 0, 3).astype(np.int32)
+    desc_mp = desc[tgt].copy()
+    for i in range(nl):
+        for b in rng.choice(256, size=int(rng.randint(0, 90)), replace=False):
+            desc_mp[i, b >> 3] ^= np.uint8(1 << (b & 7))
+    n_left_last = -1 if n_left < 0 else nl // 2
+    Tcw = np.eye(4, dtype=f32)
+    Tlw = np.eye(4, dtype=f32); Tlw[2, 3] = {"still": 0.0, "forward": 1.0, "backward": -1.0}[motion]
+    dxy = np.array([3.0, -2.0], f32)
+    Trl = np.concatenate([np.eye(3, dtype=f32), np.array([[dxy[0]], [dxy[1]], [0]], f32)], 1)
+    bounds = np.array([0, W, 0, H], f32)
+    got, rnm = Rf.search_by_projection_last_frame(kps, desc, n_left, u_right, obs_cur, grid, bounds, scale, mbf, mb, Tcw, Trl, [1, 1, 0, 0], kl, n_left_last, has_mp,
+                                                  outlier, world, obs_mp, desc_mp, Tlw, th, mono, True)
+    # the query list (INTEGRATION.md 5a, frame-to-frame variant)
+    fwd, bwd = (motion == "forward" and not mono), (motion == "backward" and not mono)
+    q, qd, src = [], [], []
+    for i in range(nl):
+        if not has_mp[i] or outlier[i] or z[i] < 0:
+            continue
+        if x[i] < 0 or x[i] > W or y[i] < 0 or y[i] > H:
+            continue
+        o = int(kl["octave"][i])
+        lo, hi = (o, -1) if fwd else (0, o) if bwd else (o - 1, o + 1)
+        fl = PC.PQ_BEST_ONLY | (PC.PQ_BLOCKS if obs_mp[i] > 0 else 0)
+        q.append((x[i], y[i], radius[i], f32(x[i] - mbf), lo, hi, fl, kl["angle"][i])); qd.append(desc_mp[i]); src.append(i)
+        if n_left >= 0:
+            q.append((f32(x[i] + dxy[0]), f32(y[i] + dxy[1]), radius[i], f32(0), lo, hi, fl | PC.PQ_RIGHT | PC.PQ_NEEDS_LEFT_WINDOW, kl["angle"][i]))
+            qd.append(desc_mp[i]); src.append(i)
+    q = np.array(q, PC.PROJ_QUERY_DTYPE)
+    pm, _, nm = O.search_by_projection(kps, desc, q, np.stack(qd), grid, n_left=n_left, u_right=u_right, taken=(obs_cur > 0).astype(np.uint8), th_high=100,
+                                       nnratio=0.9, check_orientation=True)
+    want = np.where(obs_cur >= 0, -2, -1).astype(np.int32)
+    for k in range(len(q)):
+        if pm["status"][k] in (1, 7):                                     # accepted, or accepted and later removed by the rotation check
+            want[int(pm["best_idx"][k])] = src[k]
+    for k in range(len(q)):
+        if pm["status"][k] == 7:
+            want[int(pm["best_idx"][k])] = -1
+    assert np.array_equal(got, want), "%s %s: %d rows differ" % (name, motion, int((got != want).sum()))
+    assert rnm == nm and nm > 30
+    assert (pm["status"] == 7).sum() > 0                                    # the rotation check removes some
