@@ -224,6 +224,27 @@ def cpu_oracle_rate(npairs, threads, impl="auto"):
     return 2 * npairs / dt, dt
 
 
+def cpu_two_thread_rate(npairs):
+    """The reference's own threading for one stereo frame (src/Frame.cc:119-122): left and right extraction on two threads, join, then
+    ComputeStereoMatches; one pair at a time, CPU oracle restatement."""
+    from oracle import orb_oracle as O
+    from orb_slam3_detailed_comments_kor_b200 import synth
+    pairs = [synth.stereo_pair(910000 + i, W, H) for i in range(npairs)]
+    exL, exR = O.OracleExtractor(*PARAMS), O.OracleExtractor(*PARAMS)
+    with ThreadPoolExecutor(2) as tp:
+        def one(i):
+            fl, fr = tp.submit(exL, pairs[i][0], LAP), tp.submit(exR, pairs[i][1], LAP)
+            (mL, kL, dL), (mR, kR, dR) = fl.result(), fr.result()
+            if FX > 0:
+                O.stereo_match(exL, exR, kL, dL, kR, dR, MBF, 0.0, FX)
+        one(0)
+        t0 = time.perf_counter()
+        for i in range(npairs):
+            one(i)
+        dt = time.perf_counter() - t0
+    return 2 * npairs / dt, dt
+
+
 def cv2_lines(nframes, threads):
     """Two more CPU figures with the real OpenCV (the cv2 wheel: SIMD FAST / GaussianBlur / resize, as a real ORB-SLAM3 binary has):
     `cv2_primitives_frames_per_s` = only the pixel primitives of one extraction (pyramid resize + border, FAST per 35 px cell with the
@@ -1001,6 +1022,8 @@ def main():
                    sample, dt, cores, "the reference's own ORBextractor.cc + Frame::ComputeStereoMatches (oracle/_ref; OpenCV primitives = scalar "
                    "restatements pinned to cv2 4.13)" if kind == "reference" else "CPU oracle restatement"),
                "port_frames_per_s": port_rate,
+               "one_thread_frames_per_s": cpu_oracle_rate(6, 1, kind)[0],
+               "two_threads_per_stereo_frame_frames_per_s": cpu_two_thread_rate(8)[0],
                "hamming": {"value": hrate, "unit": "descriptor_pairs/s", "sample": "%d queries x %d rows (%.1f s wall)" % (nq, ndb, hdt)}}
         cpu.update(cv2_lines(2 * cores, cores))
         from oracle import orb_oracle as O
