@@ -55,6 +55,8 @@ def lib(fma=False):
     L.ref_search_by_projection_last_frame.argtypes = [vp, vp, C.c_int, C.c_int, vp, vp, vp, vp, vp, C.c_int, C.c_float, C.c_float, vp, vp, vp, vp, C.c_int, C.c_int,
                                                       vp, vp, vp, vp, vp, vp, C.c_float, C.c_int, C.c_int, vp]
     L.ref_search_by_projection_last_frame.restype = C.c_int
+    L.ref_fuse.argtypes = [vp, vp, C.c_int, C.c_int, vp, vp, vp, vp, vp, vp, vp, C.c_int, C.c_float, vp, vp, C.c_int] + [vp] * 10 + [C.c_float, C.c_int, vp, vp]
+    L.ref_fuse.restype = C.c_int
     L.ref_kb8_project.argtypes = [vp, vp, C.c_int, vp]
     L.ref_kb8_project.restype = None
     L.ref_kb8_unproject.argtypes = [vp, vp, C.c_int, vp]
@@ -208,6 +210,23 @@ def search_by_projection_last_frame(kps, desc, n_left, u_right, obs_cur, grid4, 
                                                    p(cam4), p(kl), len(kl), int(n_left_last), p(hm), p(ol), p(w), p(om), p(dm), p(Tlw), float(th), int(mono),
                                                    int(check_orientation), p(owner))
     return owner[:len(kps)], nm
+
+
+def fuse(kps, desc, n_left, u_right, row_obs, row_bad, grid4, bounds4, scale_factors, inv_level_sigma2, bf, cam4, pose, mp, th, right):
+    """The reference's own ORBmatcher::Fuse(pKF, vpMapPoints, th, bRight) on arrays; `mp` = dict of per-map-point arrays (present, bad, in_kf,
+    world, normal, min_dist, max_dist, level, obs, desc).  Returns (fused_row[nmp], fused_how[nmp], nFused)."""
+    c = lambda a, t: None if a is None else np.ascontiguousarray(a, t)  # noqa: E731
+    p = lambda a: _ptr(a) if a is not None else None  # noqa: E731
+    f = np.float32
+    kps, desc, ur, ro, rb = c(kps, KP_DTYPE), c(desc, np.uint8), c(u_right, f), c(row_obs, np.int32), c(row_bad, np.uint8)
+    g, b, sf, isig, cam4, pose = c(grid4, f), c(bounds4, f), c(scale_factors, f), c(inv_level_sigma2, f), c(cam4, f), c(np.asarray(pose, f).reshape(12), f)
+    arrs = [c(mp["present"], np.uint8), c(mp["bad"], np.uint8), c(mp["in_kf"], np.uint8), c(mp["world"], f), c(mp["normal"], f), c(mp["min_dist"], f),
+            c(mp["max_dist"], f), c(mp["level"], np.int32), c(mp["obs"], np.int32), c(mp["desc"], np.uint8)]
+    nmp = len(arrs[0])
+    row, how = np.zeros(max(nmp, 1), np.int32), np.zeros(max(nmp, 1), np.int32)
+    nf = lib().ref_fuse(p(kps), p(desc), len(kps), int(n_left), p(ur), p(ro), p(rb), p(g), p(b), p(sf), p(isig), len(sf), float(bf), p(cam4), p(pose), nmp,
+                        *[p(a) for a in arrs], float(th), int(right), p(row), p(how))
+    return row[:nmp], how[:nmp], nf
 
 
 def kb8_project(cam, p3):

@@ -126,6 +126,22 @@ public:
     cv::Mat GetDescriptor() { return mDescriptor.clone(); }
     cv::Mat mWorldPos;
     cv::Mat GetWorldPos() { return mWorldPos.clone(); }
+    /* what ORBmatcher::Fuse reads and calls (include/MapPoint.h); the bookkeeping calls only record what happened */
+    bool inKF = false;
+    float mfMinDistance = 0, mfMaxDistance = 0;
+    cv::Mat mNormalVector;
+    int predictedLevel = 0, queryIndex = -1, rowIndex = -1, fusedRow = -1, fusedHow = 0;
+    bool IsInKeyFrame(KeyFrame*) { return inKF; }
+    float GetMinDistanceInvariance() { return mfMinDistance; }
+    float GetMaxDistanceInvariance() { return mfMaxDistance; }
+    cv::Mat GetNormal() { return mNormalVector.clone(); }
+    int PredictScale(const float&, KeyFrame*) { return predictedLevel; }
+    void AddObservation(KeyFrame*, int idx) { fusedRow = idx; fusedHow = 1; }
+    void Replace(MapPoint* other) {   /* one of the two is the candidate map point, the other the one the keypoint row holds (rowIndex >= 0) */
+        MapPoint* q = rowIndex < 0 ? this : other;
+        MapPoint* r = rowIndex < 0 ? other : this;
+        q->fusedRow = r->rowIndex; q->fusedHow = rowIndex < 0 ? 2 : 3;
+    }
 };
 
 #define FRAME_GRID_ROWS 48 /* include/Frame.h:37-38 */
@@ -176,6 +192,17 @@ public:
     GeometricCamera* mpCamera = nullptr;
     std::vector<float> mvuRight, mvScaleFactors, mvLevelSigma2;
     int N = 0;
+    /* what ORBmatcher::Fuse and KeyFrame::GetFeaturesInArea / IsInImage read on top (include/KeyFrame.h) */
+    cv::Mat mOwr;
+    cv::Mat GetRightCameraCenter() { return mOwr.clone(); }
+    float fx = 0, fy = 0, cx = 0, cy = 0, mbf = 0;
+    std::vector<float> mvInvLevelSigma2;
+    int mnGridCols = FRAME_GRID_COLS, mnGridRows = FRAME_GRID_ROWS;
+    float mfGridElementWidthInv = 0, mfGridElementHeightInv = 0, mnMinX = 0, mnMinY = 0, mnMaxX = 0, mnMaxY = 0;
+    std::vector<std::vector<std::vector<size_t>>> mGrid, mGridRight;
+    std::vector<size_t> GetFeaturesInArea(const float& x, const float& y, const float& r, const bool bRight = false) const;
+    bool IsInImage(const float& x, const float& y) const;
+    void AddMapPoint(MapPoint* pMP, const size_t& idx) { mvpMapPoints[idx] = pMP; pMP->rowIndex = (int)idx; }
     std::vector<MapPoint*> GetMapPointMatches() { return mvpMapPoints; }
     std::vector<MapPoint*> mvpMapPoints;
     DBoW2::FeatureVector mFeatVec;
@@ -197,6 +224,7 @@ public:
     int SearchForInitialization(Frame& F1, Frame& F2, std::vector<cv::Point2f>& vbPrevMatched, std::vector<int>& vnMatches12, int windowSize = 10);
     int SearchForTriangulation(KeyFrame* pKF1, KeyFrame* pKF2, cv::Mat F12, std::vector<std::pair<size_t, size_t>>& vMatchedPairs, const bool bOnlyStereo, const bool bCoarse = false);
     int SearchByProjection(Frame& CurrentFrame, const Frame& LastFrame, const float th, const bool bMono);
+    int Fuse(KeyFrame* pKF, const std::vector<MapPoint*>& vpMapPoints, const float th = 3.0, const bool bRight = false);
     float RadiusByViewingCos(const float& viewCos);
     void ComputeThreeMaxima(std::vector<int>* histo, const int L, int& ind1, int& ind2, int& ind3);
     static const int TH_LOW;
@@ -218,6 +246,8 @@ const int ORBmatcher::HISTO_LENGTH = 30;   /* src/ORBmatcher.cc:38 */
 #include "_ref/ORBmatcher_SearchForInitialization.inc"
 #include "_ref/ORBmatcher_SearchForTriangulation.inc"
 #include "_ref/ORBmatcher_SearchByProjectionLastFrame.inc"
+#include "_ref/KeyFrame_grid.inc"
+#include "_ref/ORBmatcher_Fuse.inc"
 
 /* protected members of the extractor, for the stage-level comparisons */
 struct Probe : ORBextractor {
@@ -552,6 +582,69 @@ int ref_search_by_projection_last_frame(const orc_keypoint* kps, const uint8_t* 
         owner[i] = !p ? -1 : (p >= initial.data() && p < initial.data() + n) ? -2 : (int32_t)(p - store.data());
     }
     return nm;
+}
+
+/* ORBmatcher::Fuse(pKF, vpMapPoints, th, bRight) (src/ORBmatcher.cc:1643-1841) on a keyframe and map points given as arrays.
+ *   keyframe: kps / desc [n] (rows >= n_left: the right camera), u_right [n], row_obs [n] = -1 no map point else its Observations(),
+ *   row_bad [n]; grid4, bounds4 (mnMinX, mnMaxX, mnMinY, mnMaxY), scale_factors / inv_level_sigma2 [nlevels], bf, cam4 (Pinhole), pose = Rcw[9]
+ *   tcw[3] of the camera that is searched;
+ *   map points [nmp]: present (0 = NULL pointer), bad, in_kf, world [3], normal [3], min_dist, max_dist, level (what PredictScale returns),
+ *   obs, desc_mp [32].
+ * fused_row[i] = the keypoint row map point i was fused with (-1: none), fused_how[i] = 1 AddObservation + AddMapPoint, 2 pMP->Replace(pMPinKF),
+ * 3 pMPinKF->Replace(pMP), 4 the row's point was bad (counted, nothing done).  Returns nFused. */
+int ref_fuse(const orc_keypoint* kps, const uint8_t* desc, int n, int n_left, const float* u_right, const int32_t* row_obs, const uint8_t* row_bad,
+             const float* grid4, const float* bounds4, const float* scale_factors, const float* inv_level_sigma2, int nlevels, float bf, const float* cam4,
+             const float* pose, int nmp, const uint8_t* present, const uint8_t* bad, const uint8_t* in_kf, const float* world, const float* normal,
+             const float* min_dist, const float* max_dist, const int32_t* level, const int32_t* obs, const uint8_t* desc_mp, float th, int right,
+             int32_t* fused_row, int32_t* fused_how) {
+    using namespace ORB_SLAM3;
+    ArenaScope scope;
+    Frame F;   /* the grid is built by Frame::AssignFeaturesToGrid and copied, as KeyFrame's constructor does (src/KeyFrame.cc:74-90) */
+    Frame::mnMinX = grid4[0]; Frame::mnMinY = grid4[1]; Frame::mfGridElementWidthInv = grid4[2]; Frame::mfGridElementHeightInv = grid4[3];
+    F.N = n; F.Nleft = n_left;
+    std::vector<cv::KeyPoint> all(n);
+    if (n) std::memcpy((void*)all.data(), kps, sizeof(orc_keypoint) * n);
+    if (n_left < 0) F.mvKeysUn = F.mvKeys = all;
+    else { F.mvKeys.assign(all.begin(), all.begin() + n_left); F.mvKeysRight.assign(all.begin() + n_left, all.end()); }
+    F.AssignFeaturesToGrid();
+    Pinhole camera(std::vector<float>(cam4, cam4 + 4));
+    KeyFrame kf;
+    kf.N = n; kf.NLeft = n_left;
+    kf.mvKeys = F.mvKeys; kf.mvKeysUn = F.mvKeysUn; kf.mvKeysRight = F.mvKeysRight;
+    kf.mDescriptors = cv::Mat(n, 32, CV_8UC1, (void*)desc, 32);
+    kf.mvuRight.assign(n, -1.f);
+    if (u_right) kf.mvuRight.assign(u_right, u_right + n);
+    kf.mvScaleFactors.assign(scale_factors, scale_factors + nlevels);
+    kf.mvInvLevelSigma2.assign(inv_level_sigma2, inv_level_sigma2 + nlevels);
+    kf.mnMinX = bounds4[0]; kf.mnMaxX = bounds4[1]; kf.mnMinY = bounds4[2]; kf.mnMaxY = bounds4[3];
+    kf.mfGridElementWidthInv = grid4[2]; kf.mfGridElementHeightInv = grid4[3];
+    kf.fx = cam4[0]; kf.fy = cam4[1]; kf.cx = cam4[2]; kf.cy = cam4[3]; kf.mbf = bf;
+    kf.mGrid.assign(FRAME_GRID_COLS, std::vector<std::vector<size_t>>(FRAME_GRID_ROWS));
+    kf.mGridRight = kf.mGrid;
+    for (int i = 0; i < FRAME_GRID_COLS; i++)
+        for (int j = 0; j < FRAME_GRID_ROWS; j++) { kf.mGrid[i][j] = F.mGrid[i][j]; kf.mGridRight[i][j] = F.mGridRight[i][j]; }
+    const cv::Mat Rcw = mat_from(pose, 3, 3), tcw = mat_from(pose + 9, 3, 1);
+    cv::Mat Ow = -Rcw.t() * tcw;
+    kf.mRcw = kf.mRrw = Rcw; kf.mtcw = kf.mtrw = tcw; kf.mOw = kf.mOwr = Ow;
+    kf.mpCamera = &camera; kf.mpCamera2 = &camera;
+    std::vector<MapPoint> rowPoint(n);
+    kf.mvpMapPoints.assign(n, nullptr);
+    for (int i = 0; i < n; i++)
+        if (row_obs[i] >= 0) { rowPoint[i].nObs = row_obs[i]; rowPoint[i].bad = row_bad && row_bad[i]; rowPoint[i].rowIndex = i; kf.mvpMapPoints[i] = &rowPoint[i]; }
+    std::vector<MapPoint> store(nmp);
+    std::vector<MapPoint*> vp(nmp, nullptr);
+    for (int i = 0; i < nmp; i++) {
+        MapPoint& m = store[i];
+        m.queryIndex = i; m.bad = bad[i] != 0; m.inKF = in_kf[i] != 0; m.nObs = obs[i];
+        m.mWorldPos = mat_from(world + 3 * i, 3, 1); m.mNormalVector = mat_from(normal + 3 * i, 3, 1);
+        m.mfMinDistance = min_dist[i]; m.mfMaxDistance = max_dist[i]; m.predictedLevel = level[i];
+        m.mDescriptor = cv::Mat(1, 32, CV_8UC1, (void*)(desc_mp + (size_t)i * 32), 32);
+        if (present[i]) vp[i] = &m;
+    }
+    ORBmatcher matcher(0.6f, true);
+    const int nFused = matcher.Fuse(&kf, vp, th, right != 0);
+    for (int i = 0; i < nmp; i++) { fused_row[i] = store[i].fusedRow; fused_how[i] = store[i].fusedHow; }
+    return nFused;
 }
 
 /* KannalaBrandt8::project / unproject (src/CameraModels/KannalaBrandt8.cpp:25-41, 96-125) on n points */

@@ -449,3 +449,70 @@ def test_search_by_projection_last_frame_equals_reference(name, kw, motion, mono
     assert np.array_equal(got, want), "%s %s: %d rows differ" % (name, motion, int((got != want).sum()))
     assert rnm == nm and nm > 30
     assert (pm["status"] == 7).sum() > 0                                    # the rotation check removes some
+
+
+@pytest.mark.parametrize("name,kw,right", [("stereo", dict(seed=71, n=900, stereo_gate=True), False), ("mono", dict(seed=72, n=700), False),
+                                           ("rig_left", dict(seed=73, n=900, fisheye=True), False), ("rig_right", dict(seed=74, n=900, fisheye=True), True)])
+def test_fuse_equals_reference(name, kw, right):
+    """ORBmatcher::Fuse(pKF, vpMapPoints, th, bRight) (src/ORBmatcher.cc:1643-1841, LocalMapping::SearchInNeighbors) with
+    KeyFrame::GetFeaturesInArea / IsInImage (src/KeyFrame.cc:731-780) — the reference's own bodies, compiled — against the oracle driven
+    through the query list of include/orbfe.h: ORBFE_PQ_BEST_ONLY | ORBFE_PQ_ERROR_GATE queries, nothing blocks, th_high = TH_LOW.  The
+    keypoint every map point is fused with, and nFused, must agree.  Identity pose, unit focal length, depth 1: the projection is exact."""
+    from orb_slam3_detailed_comments_kor_b200.synth import projection_cases as PC
+    f32 = np.float32
+    c = PC.make_case(nq=1, fuse=True, **kw)
+    kps, desc, grid = c["kps"], c["desc"], c["grid"]
+    n, n_left = len(kps), int(c["n_left"][0])
+    u_right = c.get("u_right") if n_left < 0 else None
+    W, H = 752.0, 480.0
+    rng = np.random.RandomState(kw["seed"] + 500)
+    scale = np.array([f32(1.2) ** i for i in range(8)], f32)
+    isig = np.array([f32(1) / (s * s) for s in scale], f32)
+    th, bf = f32(3.0), f32(40.0)
+    lo, hi = (0, n) if n_left < 0 else ((n_left, n) if right else (0, n_left))
+    nmp = 900
+    tgt = rng.randint(lo, hi, nmp)
+    level = np.minimum(7, kps["octave"][tgt] + rng.randint(0, 2, nmp)).astype(np.int32)
+    radius = (th * scale[level]).astype(f32)
+    jit = np.where(rng.uniform(size=nmp) < 0.7, 0.25, 0.9)
+    x = (kps["x"][tgt] + rng.uniform(-1, 1, nmp) * jit * radius).astype(f32)
+    y = (kps["y"][tgt] + rng.uniform(-1, 1, nmp) * jit * radius).astype(f32)
+    far = rng.uniform(size=nmp) < 0.08
+    x[far] = rng.uniform(-40, W + 40, int(far.sum())).astype(f32); y[far] = rng.uniform(-40, H + 40, int(far.sum())).astype(f32)
+    z = np.where(rng.uniform(size=nmp) < 0.05, -1.0, 1.0).astype(f32)
+    world = np.stack([x * z, y * z, z], 1).astype(f32)
+    dist = np.sqrt((world.astype(np.float64) ** 2).sum(1))
+    facing = rng.uniform(size=nmp) < 0.93
+    normal = (world / dist[:, None] * np.where(facing, 1.0, -1.0)[:, None]).astype(f32)
+    in_range = rng.uniform(size=nmp) < 0.93
+    mp = dict(present=(rng.uniform(size=nmp) < 0.95).astype(np.uint8), bad=(rng.uniform(size=nmp) < 0.05).astype(np.uint8),
+              in_kf=(rng.uniform(size=nmp) < 0.05).astype(np.uint8), world=world, normal=normal,
+              min_dist=np.where(in_range, 0.0, dist * 2).astype(f32), max_dist=np.full(nmp, 1e9, f32), level=level,
+              obs=rng.randint(0, 6, nmp).astype(np.int32), desc=desc[tgt].copy())
+    for i in range(nmp):
+        for b in rng.choice(256, size=int(rng.randint(0, 80)), replace=False):
+            mp["desc"][i, b >> 3] ^= np.uint8(1 << (b & 7))
+    row_obs = np.where(rng.uniform(size=n) < 0.5, rng.randint(0, 6, n), -1).astype(np.int32)
+    row_bad = ((rng.uniform(size=n) < 0.1) & (row_obs >= 0)).astype(np.uint8)
+    bounds = np.array([0, W, 0, H], f32)
+    pose = np.concatenate([np.eye(3, dtype=f32).reshape(9), np.zeros(3, f32)])
+    got_row, got_how, rnf = Rf.fuse(kps, desc, n_left, u_right, row_obs, row_bad, grid, bounds, scale, isig, bf, [1, 1, 0, 0], pose, mp, th, right)
+    # the query list
+    q, qd, src = [], [], []
+    for i in range(nmp):
+        if not mp["present"][i] or mp["bad"][i] or mp["in_kf"][i] or z[i] < 0:
+            continue
+        if not (0 <= x[i] < W and 0 <= y[i] < H) or not in_range[i] or not facing[i]:
+            continue
+        fl = PC.PQ_BEST_ONLY | PC.PQ_ERROR_GATE | (PC.PQ_RIGHT if right else 0)
+        q.append((x[i], y[i], radius[i], f32(x[i] - bf), level[i] - 1, level[i], fl, 0.0)); qd.append(mp["desc"][i]); src.append(i)
+    q = np.array(q, PC.PROJ_QUERY_DTYPE)
+    pm, _, nm = O.search_by_projection(kps, desc, q, np.stack(qd), grid, n_left=n_left, u_right=u_right, th_high=50, nnratio=0.6, inv_level_sigma2=isig)
+    want_row = np.full(nmp, -1, np.int32)
+    for k in range(len(q)):
+        if pm["accepted"][k]:
+            r = int(pm["best_idx"][k])
+            want_row[src[k]] = -1 if row_bad[r] else r          # a bad map point in the row: counted, nothing recorded (:1819-1828)
+    assert np.array_equal(got_row, want_row), "%s: %d map points differ" % (name, int((got_row != want_row).sum()))
+    assert rnf == int(pm["accepted"].sum()) and rnf > 100
+    assert set(np.unique(got_how)) >= {0, 1, 2, 3}                # not fused / added / replaced either way
