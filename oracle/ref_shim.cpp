@@ -22,6 +22,7 @@
 
 #include <atomic>
 #include <map>
+#include <set>
 #include <mutex>
 #include <new>
 #include <tuple>
@@ -225,6 +226,7 @@ public:
     int SearchForTriangulation(KeyFrame* pKF1, KeyFrame* pKF2, cv::Mat F12, std::vector<std::pair<size_t, size_t>>& vMatchedPairs, const bool bOnlyStereo, const bool bCoarse = false);
     int SearchByProjection(Frame& CurrentFrame, const Frame& LastFrame, const float th, const bool bMono);
     int Fuse(KeyFrame* pKF, const std::vector<MapPoint*>& vpMapPoints, const float th = 3.0, const bool bRight = false);
+    int SearchByProjection(KeyFrame* pKF, cv::Mat Scw, const std::vector<MapPoint*>& vpPoints, std::vector<MapPoint*>& vpMatched, int th, float ratioHamming = 1.0);
     float RadiusByViewingCos(const float& viewCos);
     void ComputeThreeMaxima(std::vector<int>* histo, const int L, int& ind1, int& ind2, int& ind3);
     static const int TH_LOW;
@@ -248,6 +250,7 @@ const int ORBmatcher::HISTO_LENGTH = 30;   /* src/ORBmatcher.cc:38 */
 #include "_ref/ORBmatcher_SearchByProjectionLastFrame.inc"
 #include "_ref/KeyFrame_grid.inc"
 #include "_ref/ORBmatcher_Fuse.inc"
+#include "_ref/ORBmatcher_SearchByProjectionSim3.inc"
 
 /* protected members of the extractor, for the stage-level comparisons */
 struct Probe : ORBextractor {
@@ -645,6 +648,54 @@ int ref_fuse(const orc_keypoint* kps, const uint8_t* desc, int n, int n_left, co
     const int nFused = matcher.Fuse(&kf, vp, th, right != 0);
     for (int i = 0; i < nmp; i++) { fused_row[i] = store[i].fusedRow; fused_how[i] = store[i].fusedHow; }
     return nFused;
+}
+
+/* ORBmatcher::SearchByProjection(pKF, Scw, vpPoints, vpMatched, th, ratioHamming) (src/ORBmatcher.cc:473-586) on arrays.  matched_in [n]: -1 the
+ * row has no match yet, -2 some other map point, k >= 0 candidate k itself (so that it is "already found").  Scw [16].  owner as elsewhere. */
+int ref_search_by_projection_sim3(const orc_keypoint* kps, const uint8_t* desc, int n, const int32_t* matched_in, const float* grid4, const float* bounds4,
+                                  const float* scale_factors, int nlevels, const float* cam4, const float* Scw, int nmp, const uint8_t* bad, const float* world,
+                                  const float* normal, const float* min_dist, const float* max_dist, const int32_t* level, const uint8_t* desc_mp, int th,
+                                  float ratio_hamming, int32_t* owner) {
+    using namespace ORB_SLAM3;
+    ArenaScope scope;
+    Frame F;
+    Frame::mnMinX = grid4[0]; Frame::mnMinY = grid4[1]; Frame::mfGridElementWidthInv = grid4[2]; Frame::mfGridElementHeightInv = grid4[3];
+    F.N = n; F.Nleft = -1;
+    F.mvKeysUn.resize(n);
+    if (n) std::memcpy((void*)F.mvKeysUn.data(), kps, sizeof(orc_keypoint) * n);
+    F.mvKeys = F.mvKeysUn;
+    F.AssignFeaturesToGrid();
+    Pinhole camera(std::vector<float>(cam4, cam4 + 4));
+    KeyFrame kf;
+    kf.N = n; kf.NLeft = -1;
+    kf.mvKeys = kf.mvKeysUn = F.mvKeysUn;
+    kf.mDescriptors = cv::Mat(n, 32, CV_8UC1, (void*)desc, 32);
+    kf.mvScaleFactors.assign(scale_factors, scale_factors + nlevels);
+    kf.mnMinX = bounds4[0]; kf.mnMaxX = bounds4[1]; kf.mnMinY = bounds4[2]; kf.mnMaxY = bounds4[3];
+    kf.mfGridElementWidthInv = grid4[2]; kf.mfGridElementHeightInv = grid4[3];
+    kf.fx = cam4[0]; kf.fy = cam4[1]; kf.cx = cam4[2]; kf.cy = cam4[3];
+    kf.mGrid.assign(FRAME_GRID_COLS, std::vector<std::vector<size_t>>(FRAME_GRID_ROWS));
+    kf.mGridRight = kf.mGrid;
+    for (int i = 0; i < FRAME_GRID_COLS; i++)
+        for (int j = 0; j < FRAME_GRID_ROWS; j++) kf.mGrid[i][j] = F.mGrid[i][j];
+    kf.mpCamera = &camera;
+    std::vector<MapPoint> store(nmp);
+    std::vector<MapPoint*> vp(nmp);
+    for (int i = 0; i < nmp; i++) {
+        MapPoint& m = store[i];
+        m.bad = bad[i] != 0;
+        m.mWorldPos = mat_from(world + 3 * i, 3, 1); m.mNormalVector = mat_from(normal + 3 * i, 3, 1);
+        m.mfMinDistance = min_dist[i]; m.mfMaxDistance = max_dist[i]; m.predictedLevel = level[i];
+        m.mDescriptor = cv::Mat(1, 32, CV_8UC1, (void*)(desc_mp + (size_t)i * 32), 32);
+        vp[i] = &m;
+    }
+    MapPoint other;
+    std::vector<MapPoint*> matched(n, nullptr);
+    for (int i = 0; i < n; i++) matched[i] = matched_in[i] == -1 ? nullptr : matched_in[i] == -2 ? &other : &store[matched_in[i]];
+    ORBmatcher matcher(0.75f, true);
+    const int nm = matcher.SearchByProjection(&kf, mat_from(Scw, 4, 4), vp, matched, th, ratio_hamming);
+    for (int i = 0; i < n; i++) owner[i] = !matched[i] ? -1 : matched[i] == &other ? -2 : (int32_t)(matched[i] - store.data());
+    return nm;
 }
 
 /* KannalaBrandt8::project / unproject (src/CameraModels/KannalaBrandt8.cpp:25-41, 96-125) on n points */

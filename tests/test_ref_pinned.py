@@ -516,3 +516,58 @@ def test_fuse_equals_reference(name, kw, right):
     assert np.array_equal(got_row, want_row), "%s: %d map points differ" % (name, int((got_row != want_row).sum()))
     assert rnf == int(pm["accepted"].sum()) and rnf > 100
     assert set(np.unique(got_how)) >= {0, 1, 2, 3}                # not fused / added / replaced either way
+
+
+@pytest.mark.parametrize("seed,ratio", [(81, 1.0), (82, 0.8), (83, 1.5)])
+def test_search_by_projection_sim3_equals_reference(seed, ratio):
+    """ORBmatcher::SearchByProjection(pKF, Scw, vpPoints, vpMatched, th, ratioHamming) (src/ORBmatcher.cc:473-586, LoopClosing) — the reference's
+    body, compiled — against the oracle: ORBFE_PQ_BEST_ONLY | ORBFE_PQ_BLOCKS queries, rows that are already matched given as `taken`,
+    th_high = floor(TH_LOW * ratioHamming).  Scw = 2 * [I | 0]: the similarity is decomposed exactly."""
+    from orb_slam3_detailed_comments_kor_b200.synth import projection_cases as PC
+    f32 = np.float32
+    c = PC.make_case(nq=1, seed=seed, n=800)
+    kps, desc, grid = c["kps"], c["desc"], c["grid"]
+    n = len(kps)
+    W, H = 752.0, 480.0
+    rng = np.random.RandomState(seed + 300)
+    scale = np.array([f32(1.2) ** i for i in range(8)], f32)
+    th = 4
+    nmp = 900
+    hot = rng.choice(n, 15, replace=False)
+    tgt = np.where(rng.uniform(size=nmp) < 0.3, hot[rng.randint(0, 15, nmp)], rng.randint(0, n, nmp))
+    level = np.minimum(7, kps["octave"][tgt] + rng.randint(0, 2, nmp)).astype(np.int32)
+    radius = (f32(th) * scale[level]).astype(f32)
+    x = (kps["x"][tgt] + rng.uniform(-0.7, 0.7, nmp) * radius).astype(f32)
+    y = (kps["y"][tgt] + rng.uniform(-0.7, 0.7, nmp) * radius).astype(f32)
+    far = rng.uniform(size=nmp) < 0.08
+    x[far] = rng.uniform(-40, W + 40, int(far.sum())).astype(f32); y[far] = rng.uniform(-40, H + 40, int(far.sum())).astype(f32)
+    z = np.where(rng.uniform(size=nmp) < 0.05, -1.0, 1.0).astype(f32)
+    world = np.stack([x * z, y * z, z], 1).astype(f32)
+    dist = np.sqrt((world.astype(np.float64) ** 2).sum(1))
+    facing = rng.uniform(size=nmp) < 0.93
+    in_range = rng.uniform(size=nmp) < 0.93
+    mp = dict(bad=(rng.uniform(size=nmp) < 0.05).astype(np.uint8), world=world, normal=(world / dist[:, None] * np.where(facing, 1.0, -1.0)[:, None]).astype(f32),
+              min_dist=np.where(in_range, 0.0, dist * 2).astype(f32), max_dist=np.full(nmp, 1e9, f32), level=level, desc=desc[tgt].copy())
+    for i in range(nmp):
+        for b in rng.choice(256, size=int(rng.randint(0, 90)), replace=False):
+            mp["desc"][i, b >> 3] ^= np.uint8(1 << (b & 7))
+    matched_in = np.where(rng.uniform(size=n) < 0.1, -2, -1).astype(np.int32)
+    found = rng.choice(nmp, 40, replace=False)                               # candidates that are already matched somewhere in the keyframe
+    rows = rng.choice(n, 40, replace=False)
+    matched_in[rows] = found
+    Scw = np.diag([2, 2, 2, 1]).astype(f32)
+    got, rnm = Rf.search_by_projection_sim3(kps, desc, matched_in, grid, [0, W, 0, H], scale, [1, 1, 0, 0], Scw, mp, th, ratio)
+    already = set(int(v) for v in found)
+    q, qd, src = [], [], []
+    for i in range(nmp):
+        if mp["bad"][i] or i in already or z[i] < 0 or not (0 <= x[i] < W and 0 <= y[i] < H) or not in_range[i] or not facing[i]:
+            continue
+        q.append((x[i], y[i], radius[i], 0.0, level[i] - 1, level[i], PC.PQ_BEST_ONLY | PC.PQ_BLOCKS, 0.0)); qd.append(mp["desc"][i]); src.append(i)
+    q = np.array(q, PC.PROJ_QUERY_DTYPE)
+    pm, _, nm = O.search_by_projection(kps, desc, q, np.stack(qd), grid, taken=(matched_in != -1).astype(np.uint8), th_high=int(np.floor(50 * ratio)), nnratio=0.75)
+    want = matched_in.copy()
+    for k in range(len(q)):
+        if pm["accepted"][k]:
+            want[int(pm["best_idx"][k])] = src[k]
+    assert np.array_equal(got, want), "%d rows differ" % int((got != want).sum())
+    assert rnm == nm and nm > 100
