@@ -431,29 +431,36 @@ static __host__ __device__ __forceinline__ bool fast_is_corner_vals(int v, const
  * m = max(v - min_arcs(max_arc r), max_arcs(min_arc r) - v).  Besides being cheaper this keeps every min/max
  * operand a plain non-negated register: nvcc 12.9 folds a negation into VIMNMX3 on sm_100a and the result
  * loses the sign (found by tools/fast_device_test3.cu: max(m, max(lo, -hi)) returned max(m, lo, hi)). */
+#ifdef __CUDA_ARCH__
+#define MIN3(a, b, c) __vimin3_s32((a), (b), (c))   /* one VIMNMX3; written as min(min()) nvcc 12.9 emits two VIMNMX for most of them */
+#define MAX3(a, b, c) __vimax3_s32((a), (b), (c))
+#else
+#define MIN3(a, b, c) min(min((a), (b)), (c))
+#define MAX3(a, b, c) max(max((a), (b)), (c))
+#endif
 static __host__ __device__ __forceinline__ int fast_score_vals(int v, const int (&r)[16]) {
     /* arcs of nine as three runs of three: 16 + 16 three-input min (max) per polarity, then a three-input reduction */
     int lo3[16], hi3[16];
 #pragma unroll
     for (int k = 0; k < 16; k++) {
-        lo3[k] = min(min(r[k], r[(k + 1) & 15]), r[(k + 2) & 15]);
-        hi3[k] = max(max(r[k], r[(k + 1) & 15]), r[(k + 2) & 15]);
+        lo3[k] = MIN3(r[k], r[(k + 1) & 15], r[(k + 2) & 15]);
+        hi3[k] = MAX3(r[k], r[(k + 1) & 15], r[(k + 2) & 15]);
     }
     int lo9[16], hi9[16];
 #pragma unroll
     for (int k = 0; k < 16; k++) {
-        lo9[k] = min(min(lo3[k], lo3[(k + 3) & 15]), lo3[(k + 6) & 15]);
-        hi9[k] = max(max(hi3[k], hi3[(k + 3) & 15]), hi3[(k + 6) & 15]);
+        lo9[k] = MIN3(lo3[k], lo3[(k + 3) & 15], lo3[(k + 6) & 15]);
+        hi9[k] = MAX3(hi3[k], hi3[(k + 3) & 15], hi3[(k + 6) & 15]);
     }
     int a[6], b[6];
 #pragma unroll
     for (int k = 0; k < 5; k++) {
-        a[k] = max(max(lo9[3 * k], lo9[3 * k + 1]), lo9[3 * k + 2]);
-        b[k] = min(min(hi9[3 * k], hi9[3 * k + 1]), hi9[3 * k + 2]);
+        a[k] = MAX3(lo9[3 * k], lo9[3 * k + 1], lo9[3 * k + 2]);
+        b[k] = MIN3(hi9[3 * k], hi9[3 * k + 1], hi9[3 * k + 2]);
     }
     a[5] = lo9[15]; b[5] = hi9[15];
-    const int maxOfMin = max(max(max(a[0], a[1]), a[2]), max(max(a[3], a[4]), a[5]));
-    const int minOfMax = min(min(min(b[0], b[1]), b[2]), min(min(b[3], b[4]), b[5]));
+    const int maxOfMin = max(MAX3(a[0], a[1], a[2]), MAX3(a[3], a[4], a[5]));
+    const int minOfMax = min(MIN3(b[0], b[1], b[2]), MIN3(b[3], b[4], b[5]));
     const int dark = v - minOfMax, bright = maxOfMin - v;
     return (dark > bright ? dark : bright) - 1;
 }
