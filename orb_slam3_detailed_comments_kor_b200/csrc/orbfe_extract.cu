@@ -680,7 +680,10 @@ __global__ void __launch_bounds__(FAST_NT, 8) k_fast_cells_list(const __grid_con
 #ifndef FS_WARPS
 #define FS_WARPS 1
 #endif
-#define FS_R 8          /* rows per compaction chunk */
+#ifndef FS_R
+#define FS_R 8          /* rows per compaction chunk: a multiple of 8 (one 32-bit survivor mask per lane and 8 rows) */
+#endif
+#define FS_H (FS_R / 8)
 #define FS_COLS 120     /* candidate columns per strip (lanes 1..30; lanes 0 and 31 carry the 4 px halos) */
 
 /* One warp = one strip (120 columns x up to 32 rows; one strip = one CTA) of one level of one frame; warps are independent (no block
@@ -728,21 +731,29 @@ __global__ void __launch_bounds__(FS_WARPS * 32, 32 / FS_WARPS) k_fast_stream(co
         /* 1. sieve, one row per step: buffer rows r (y-3), r+3 (y), r+6 (y+3, fetched one step earlier).  The survivors of
          *    my four columns collect in hm, one nibble per row: the high half of h * 0x02040810 holds bits 7, 15, 23, 31 of h
          *    in its low nibble, and the funnel shift keeps exactly that nibble */
-        uint32_t hm = 0;
-        for (int r = 0; r < rows; r++) {
-            const uint32_t top = nxt;
-            p += pitch;
-            nxt = __ldg(reinterpret_cast<const uint32_t*>(p));
-            buf[(r + 6) * FS_PW + lane] = top;
-            const uint32_t cen = buf[(r + 3) * FS_PW + lane], bot = buf[r * FS_PW + lane];
-            const uint32_t lw = __shfl_up_sync(0xFFFFFFFFu, cen, 1), rw = __shfl_down_sync(0xFFFFFFFFu, cen, 1);
-            const uint32_t h = fast_sieve4(cen, top, bot, __byte_perm(lw, cen, 0x4321), __byte_perm(cen, rw, 0x6543), k127mt) & vmask;
-            hm = __funnelshift_r(hm, __umulhi(h, 0x02040810u), 4);
+        uint32_t hmv[FS_H];
+        int cnt = 0;
+#pragma unroll
+        for (int g = 0; g < FS_H; g++) {
+            const int gr = min(8, rows - 8 * g);   /* rows of this group of eight (<= 0: none) */
+            uint32_t hm = 0;
+            for (int rr = 0; rr < gr; rr++) {
+                const int r = 8 * g + rr;
+                const uint32_t top = nxt;
+                p += pitch;
+                nxt = __ldg(reinterpret_cast<const uint32_t*>(p));
+                buf[(r + 6) * FS_PW + lane] = top;
+                const uint32_t cen = buf[(r + 3) * FS_PW + lane], bot = buf[r * FS_PW + lane];
+                const uint32_t lw = __shfl_up_sync(0xFFFFFFFFu, cen, 1), rw = __shfl_down_sync(0xFFFFFFFFu, cen, 1);
+                const uint32_t h = fast_sieve4(cen, top, bot, __byte_perm(lw, cen, 0x4321), __byte_perm(cen, rw, 0x6543), k127mt) & vmask;
+                hm = __funnelshift_r(hm, __umulhi(h, 0x02040810u), 4);
+            }
+            hm = gr > 0 ? hm >> (4 * (8 - gr)) : 0u;   /* bit 4r + k: row r of the group, column k of my word */
+            hmv[g] = hm;
+            cnt += __popc(hm);
         }
-        hm >>= 4 * (FS_R - rows);   /* bit 4r + k: row r of the chunk, column k of my word */
         __syncwarp();
         /* 2. compaction: one warp scan of the per-lane counts gives every lane its run of queue slots */
-        const int cnt = __popc(hm);
         int incl = cnt;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
@@ -752,11 +763,14 @@ __global__ void __launch_bounds__(FS_WARPS * 32, 32 / FS_WARPS) k_fast_stream(co
         const int n = __shfl_sync(0xFFFFFFFFu, incl, 31);
         {
             int pos = incl - cnt;
-            uint32_t m = hm;
-            while (m) {
-                const int bit = __ffs(m) - 1;
-                m &= m - 1;
-                q[pos++] = (uint16_t)((bit >> 2) * (4 * FS_PW) + 4 * lane + (bit & 3));   /* byte offset from bufb */
+#pragma unroll
+            for (int g = 0; g < FS_H; g++) {
+                uint32_t m = hmv[g];
+                while (m) {
+                    const int bit = __ffs(m) - 1;
+                    m &= m - 1;
+                    q[pos++] = (uint16_t)((8 * g + (bit >> 2)) * (4 * FS_PW) + 4 * lane + (bit & 3));   /* byte offset from bufb */
+                }
             }
         }
         if (n > 0) {
