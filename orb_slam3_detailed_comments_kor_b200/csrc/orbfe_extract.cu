@@ -695,7 +695,10 @@ __global__ void __launch_bounds__(FAST_NT, 8) k_fast_cells_list(const __grid_con
  * k_fast_nms then does the cell-local non-maximum suppression and ordering. */
 #define FS_BROWS (FS_R + 6)   /* rows yc-3 .. yc+FS_R+2 of the current chunk */
 #define FS_PW 33               /* words per buffered row: 32 + 1 so that equal columns of different rows hit different banks */
-__global__ void __launch_bounds__(FS_WARPS * 32, 32 / FS_WARPS) k_fast_stream(const __grid_constant__ ExDesc d, ExBuffers b, int stripBase, int nStrips) {
+#ifndef FS_MINB
+#define FS_MINB (32 / FS_WARPS)
+#endif
+__global__ void __launch_bounds__(FS_WARPS * 32, FS_MINB) k_fast_stream(const __grid_constant__ ExDesc d, ExBuffers b, int stripBase, int nStrips) {
     __shared__ __align__(16) uint32_t s_buf[FS_WARPS][FS_BROWS][FS_PW];
     __shared__ uint16_t s_q[FS_WARPS][FS_R * FS_COLS + 32];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
