@@ -543,7 +543,7 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--pairs", type=int, default=256, help="stereo pairs per GPU per step")
+    ap.add_argument("--pairs", type=int, default=512, help="stereo pairs per GPU per step")
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--hamming-queries", type=int, default=4096)
     ap.add_argument("--hamming-db", type=int, default=1 << 20)
