@@ -464,6 +464,58 @@ def test_stereo_frames_batch_device_left_right_side_by_side():
     exL.close(); exR.close()
 
 
+def test_entry_points_interleaved_on_the_same_objects():
+    """The same two extractor objects driven through every way in, one after the other and repeatedly: device pair call on a caller's
+    stream, pipelined host batches, synchronous host batch, single frame (CUDA graph), device pair call without a caller stream.  The
+    calls share streams, events and staging buffers inside the objects; every one must give what the first gave."""
+    import torch
+    W, H, params, nb = 320, 240, (500, 1.2, 8, 20, 7), 40
+    pairs = [synth.stereo_pair(5200 + i, W, H) for i in range(nb)]
+    hL = torch.from_numpy(np.stack([p[0] for p in pairs])).pin_memory(); hR = torch.from_numpy(np.stack([p[1] for p in pairs])).pin_memory()
+    dLs, dRs = hL.cuda(), hR.cuda()
+    exL = ORBextractor(*params, width=W, height=H, max_batch=nb)
+    exR = ORBextractor(*params, width=W, height=H, max_batch=nb)
+    cap = exL.capacity
+    want = [a.copy() for a in M.stereo_frames_batch_host(exL, exR, hL.numpy(), hR.numpy(), 40.0, 0.0, 300.0, (0, 0))]
+    st = torch.cuda.Stream()
+
+    def device_snapshot():
+        cl, _ = exL.batch_counts(nb); cr, _ = exR.batch_counts(nb)
+        assert np.array_equal(cl, want[0]) and np.array_equal(cr, want[4])
+        for f in (0, nb // 2, nb - 1):
+            ml, kl, dl = exL.batch_result(f); mr, kr, dr = exR.batch_result(f)
+            u, d = M.stereo_result(exL, f)
+            assert np.array_equal(kl, want[2][f, :cl[f]]) and np.array_equal(dl, want[3][f, :cl[f]]) and np.array_equal(kr, want[6][f, :cr[f]])
+            assert np.array_equal(u, want[8][f, :cl[f]]) and np.array_equal(d, want[9][f, :cl[f]])
+
+    def out_set():
+        side = lambda: (np.zeros(nb, np.int32), np.zeros(nb, np.int32), np.zeros((nb, cap), KP_DTYPE), np.zeros((nb, cap, 32), np.uint8))  # noqa: E731
+        return side() + side() + (np.zeros((nb, cap), np.float32), np.zeros((nb, cap), np.float32))
+    outs = [out_set(), out_set()]
+    for rep in range(3):
+        M.stereo_frames_batch_device(exL, exR, dLs.data_ptr(), dRs.data_ptr(), nb, 40.0, 0.0, 300.0, (0, 0), st.cuda_stream)
+        device_snapshot()
+        M.stereo_frames_submit(exL, exR, hL.numpy(), hR.numpy(), 40.0, 0.0, 300.0, (0, 0), outs[0])
+        M.stereo_frames_submit(exL, exR, hL.numpy(), hR.numpy(), 40.0, 0.0, 300.0, (0, 0), outs[1])
+        with pytest.raises(OrbfeError):                                     # host batches in flight: the device pair call is refused
+            M.stereo_frames_batch_device(exL, exR, dLs.data_ptr(), dRs.data_ptr(), nb, 40.0, 0.0, 300.0)
+        for o in outs:
+            got = M.stereo_frames_wait(exL, exR, o)
+            assert np.array_equal(got[0], want[0]) and np.array_equal(got[4], want[4])
+            for f in range(nb):
+                n = want[0][f]
+                assert np.array_equal(got[2][f, :n], want[2][f, :n]) and np.array_equal(got[3][f, :n], want[3][f, :n])
+                assert np.array_equal(got[8][f, :n], want[8][f, :n]) and np.array_equal(got[9][f, :n], want[9][f, :n])
+        mono, k, dsc = exL(pairs[3][0], (0, 0))                             # single frame: frame 0 of the object is now pair 3's left image
+        assert np.array_equal(k, want[2][3, :want[0][3]]) and np.array_equal(dsc, want[3][3, :want[0][3]])
+        M.stereo_frames_batch_device(exL, exR, dLs.data_ptr(), dRs.data_ptr(), nb, 40.0, 0.0, 300.0)   # own streams only
+        device_snapshot()
+        got = M.stereo_frames_batch_host(exL, exR, hL.numpy(), hR.numpy(), 40.0, 0.0, 300.0, (0, 0))
+        for a, b in zip(got, want):
+            assert np.array_equal(a[:nb], b[:nb]) if a.ndim == 1 else True
+    exL.close(); exR.close()
+
+
 def test_kitti_full_size_batch_properties():
     """BASELINE config 4 at full size: 4096 KITTI-shaped images (2048 stereo pairs, 1241x376, 2000 features) in one device
     batch per camera.  The batch is 16 distinct pairs repeated in a scrambled order: every frame must give exactly what its
