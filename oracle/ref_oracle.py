@@ -59,6 +59,8 @@ def lib(fma=False):
     L.ref_fuse.restype = C.c_int
     L.ref_search_by_projection_sim3.argtypes = [vp, vp, C.c_int, vp, vp, vp, vp, C.c_int, vp, vp, C.c_int, vp, vp, vp, vp, vp, vp, vp, C.c_int, C.c_float, vp]
     L.ref_search_by_projection_sim3.restype = C.c_int
+    L.ref_fuse_sim3.argtypes = [vp, vp, C.c_int, vp, vp, vp, vp, C.c_int, vp, vp, C.c_int, vp, vp, vp, vp, vp, vp, vp, C.c_float, vp, vp]
+    L.ref_fuse_sim3.restype = C.c_int
     L.ref_kb8_project.argtypes = [vp, vp, C.c_int, vp]
     L.ref_kb8_project.restype = None
     L.ref_kb8_unproject.argtypes = [vp, vp, C.c_int, vp]
@@ -241,6 +243,19 @@ def search_by_projection_sim3(kps, desc, matched_in, grid4, bounds4, scale_facto
     nm = lib().ref_search_by_projection_sim3(_ptr(kps), _ptr(desc), len(kps), _ptr(mi), _ptr(g), _ptr(b), _ptr(sf), len(sf), _ptr(cam4), _ptr(Scw), len(arrs[0]),
                                              *[_ptr(a) for a in arrs], int(th), float(ratio_hamming), _ptr(owner))
     return owner[:len(kps)], nm
+
+
+def fuse_sim3(kps, desc, row_state, grid4, bounds4, scale_factors, cam4, Scw, mp, th):
+    """The reference's own ORBmatcher::Fuse(pKF, Scw, vpPoints, th, vpReplacePoint) on arrays.  Returns (fused_row[nmp], replaced[nmp], nFused)."""
+    c = lambda a, t: np.ascontiguousarray(a, t)  # noqa: E731
+    f = np.float32
+    kps, desc, rs, g, b, sf, cam4, Scw = c(kps, KP_DTYPE), c(desc, np.uint8), c(row_state, np.int32), c(grid4, f), c(bounds4, f), c(scale_factors, f), c(cam4, f), c(np.asarray(Scw, f).reshape(16), f)
+    arrs = [c(mp["bad"], np.uint8), c(mp["world"], f), c(mp["normal"], f), c(mp["min_dist"], f), c(mp["max_dist"], f), c(mp["level"], np.int32), c(mp["desc"], np.uint8)]
+    nmp = len(arrs[0])
+    row, rep = np.zeros(max(nmp, 1), np.int32), np.zeros(max(nmp, 1), np.int32)
+    nf = lib().ref_fuse_sim3(_ptr(kps), _ptr(desc), len(kps), _ptr(rs), _ptr(g), _ptr(b), _ptr(sf), len(sf), _ptr(cam4), _ptr(Scw), nmp, *[_ptr(a) for a in arrs],
+                             float(th), _ptr(row), _ptr(rep))
+    return row[:nmp], rep[:nmp], nf
 
 
 def kb8_project(cam, p3):

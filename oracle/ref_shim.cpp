@@ -204,6 +204,7 @@ public:
     std::vector<size_t> GetFeaturesInArea(const float& x, const float& y, const float& r, const bool bRight = false) const;
     bool IsInImage(const float& x, const float& y) const;
     void AddMapPoint(MapPoint* pMP, const size_t& idx) { mvpMapPoints[idx] = pMP; pMP->rowIndex = (int)idx; }
+    std::set<MapPoint*> GetMapPoints() { std::set<MapPoint*> r; for (MapPoint* m : mvpMapPoints) if (m && !m->isBad()) r.insert(m); return r; }   /* src/KeyFrame.cc:392-405 */
     std::vector<MapPoint*> GetMapPointMatches() { return mvpMapPoints; }
     std::vector<MapPoint*> mvpMapPoints;
     DBoW2::FeatureVector mFeatVec;
@@ -227,6 +228,7 @@ public:
     int SearchByProjection(Frame& CurrentFrame, const Frame& LastFrame, const float th, const bool bMono);
     int Fuse(KeyFrame* pKF, const std::vector<MapPoint*>& vpMapPoints, const float th = 3.0, const bool bRight = false);
     int SearchByProjection(KeyFrame* pKF, cv::Mat Scw, const std::vector<MapPoint*>& vpPoints, std::vector<MapPoint*>& vpMatched, int th, float ratioHamming = 1.0);
+    int Fuse(KeyFrame* pKF, cv::Mat Scw, const std::vector<MapPoint*>& vpPoints, float th, std::vector<MapPoint*>& vpReplacePoint);
     float RadiusByViewingCos(const float& viewCos);
     void ComputeThreeMaxima(std::vector<int>* histo, const int L, int& ind1, int& ind2, int& ind3);
     static const int TH_LOW;
@@ -251,6 +253,7 @@ const int ORBmatcher::HISTO_LENGTH = 30;   /* src/ORBmatcher.cc:38 */
 #include "_ref/KeyFrame_grid.inc"
 #include "_ref/ORBmatcher_Fuse.inc"
 #include "_ref/ORBmatcher_SearchByProjectionSim3.inc"
+#include "_ref/ORBmatcher_FuseSim3.inc"
 
 /* protected members of the extractor, for the stage-level comparisons */
 struct Probe : ORBextractor {
@@ -696,6 +699,63 @@ int ref_search_by_projection_sim3(const orc_keypoint* kps, const uint8_t* desc, 
     const int nm = matcher.SearchByProjection(&kf, mat_from(Scw, 4, 4), vp, matched, th, ratio_hamming);
     for (int i = 0; i < n; i++) owner[i] = !matched[i] ? -1 : matched[i] == &other ? -2 : (int32_t)(matched[i] - store.data());
     return nm;
+}
+
+/* ORBmatcher::Fuse(pKF, Scw, vpPoints, th, vpReplacePoint) (src/ORBmatcher.cc:1843-1965) on arrays.  row_state [n]: -1 the row has no map point,
+ * -2 another map point, -3 another, bad one, k >= 0 candidate k itself (so that it is in pKF->GetMapPoints()).
+ * fused_row[i] = the row candidate i was fused with (added, or to be replaced by the row's point), -1 none; replaced[i] = 1 iff vpReplacePoint[i]
+ * was set.  Returns nFused. */
+int ref_fuse_sim3(const orc_keypoint* kps, const uint8_t* desc, int n, const int32_t* row_state, const float* grid4, const float* bounds4,
+                  const float* scale_factors, int nlevels, const float* cam4, const float* Scw, int nmp, const uint8_t* bad, const float* world,
+                  const float* normal, const float* min_dist, const float* max_dist, const int32_t* level, const uint8_t* desc_mp, float th,
+                  int32_t* fused_row, int32_t* replaced) {
+    using namespace ORB_SLAM3;
+    ArenaScope scope;
+    Frame F;
+    Frame::mnMinX = grid4[0]; Frame::mnMinY = grid4[1]; Frame::mfGridElementWidthInv = grid4[2]; Frame::mfGridElementHeightInv = grid4[3];
+    F.N = n; F.Nleft = -1;
+    F.mvKeysUn.resize(n);
+    if (n) std::memcpy((void*)F.mvKeysUn.data(), kps, sizeof(orc_keypoint) * n);
+    F.mvKeys = F.mvKeysUn;
+    F.AssignFeaturesToGrid();
+    Pinhole camera(std::vector<float>(cam4, cam4 + 4));
+    KeyFrame kf;
+    kf.N = n; kf.NLeft = -1;
+    kf.mvKeys = kf.mvKeysUn = F.mvKeysUn;
+    kf.mDescriptors = cv::Mat(n, 32, CV_8UC1, (void*)desc, 32);
+    kf.mvScaleFactors.assign(scale_factors, scale_factors + nlevels);
+    kf.mnMinX = bounds4[0]; kf.mnMaxX = bounds4[1]; kf.mnMinY = bounds4[2]; kf.mnMaxY = bounds4[3];
+    kf.mfGridElementWidthInv = grid4[2]; kf.mfGridElementHeightInv = grid4[3];
+    kf.fx = cam4[0]; kf.fy = cam4[1]; kf.cx = cam4[2]; kf.cy = cam4[3];
+    kf.mGrid.assign(FRAME_GRID_COLS, std::vector<std::vector<size_t>>(FRAME_GRID_ROWS));
+    kf.mGridRight = kf.mGrid;
+    for (int i = 0; i < FRAME_GRID_COLS; i++)
+        for (int j = 0; j < FRAME_GRID_ROWS; j++) kf.mGrid[i][j] = F.mGrid[i][j];
+    kf.mpCamera = &camera;
+    std::vector<MapPoint> store(nmp), rowPoint(n);
+    std::vector<MapPoint*> vp(nmp), repl(nmp, nullptr);
+    for (int i = 0; i < nmp; i++) {
+        MapPoint& m = store[i];
+        m.queryIndex = i; m.bad = bad[i] != 0;
+        m.mWorldPos = mat_from(world + 3 * i, 3, 1); m.mNormalVector = mat_from(normal + 3 * i, 3, 1);
+        m.mfMinDistance = min_dist[i]; m.mfMaxDistance = max_dist[i]; m.predictedLevel = level[i];
+        m.mDescriptor = cv::Mat(1, 32, CV_8UC1, (void*)(desc_mp + (size_t)i * 32), 32);
+        vp[i] = &m;
+    }
+    kf.mvpMapPoints.assign(n, nullptr);
+    for (int i = 0; i < n; i++) {
+        if (row_state[i] == -1) continue;
+        if (row_state[i] >= 0) { kf.mvpMapPoints[i] = &store[row_state[i]]; store[row_state[i]].rowIndex = i; continue; }
+        rowPoint[i].rowIndex = i; rowPoint[i].bad = row_state[i] == -3;
+        kf.mvpMapPoints[i] = &rowPoint[i];
+    }
+    ORBmatcher matcher(0.8f, true);
+    const int nFused = matcher.Fuse(&kf, mat_from(Scw, 4, 4), vp, th, repl);
+    for (int i = 0; i < nmp; i++) {
+        replaced[i] = repl[i] != nullptr;
+        fused_row[i] = repl[i] ? repl[i]->rowIndex : store[i].fusedRow;
+    }
+    return nFused;
 }
 
 /* KannalaBrandt8::project / unproject (src/CameraModels/KannalaBrandt8.cpp:25-41, 96-125) on n points */

@@ -571,3 +571,56 @@ def test_search_by_projection_sim3_equals_reference(seed, ratio):
             want[int(pm["best_idx"][k])] = src[k]
     assert np.array_equal(got, want), "%d rows differ" % int((got != want).sum())
     assert rnm == nm and nm > 100
+
+
+@pytest.mark.parametrize("seed", [91, 92])
+def test_fuse_sim3_equals_reference(seed):
+    """ORBmatcher::Fuse(pKF, Scw, vpPoints, th, vpReplacePoint) (src/ORBmatcher.cc:1843-1965, LoopClosing::SearchAndFuse) — the reference's body,
+    compiled — against the oracle: ORBFE_PQ_BEST_ONLY queries, nothing blocks, no gate, th_high = TH_LOW."""
+    from orb_slam3_detailed_comments_kor_b200.synth import projection_cases as PC
+    f32 = np.float32
+    c = PC.make_case(nq=1, seed=seed, n=800)
+    kps, desc, grid = c["kps"], c["desc"], c["grid"]
+    n = len(kps)
+    W, H = 752.0, 480.0
+    rng = np.random.RandomState(seed + 700)
+    scale = np.array([f32(1.2) ** i for i in range(8)], f32)
+    th, nmp = f32(4.0), 900
+    hot = rng.choice(n, 15, replace=False)
+    tgt = np.where(rng.uniform(size=nmp) < 0.3, hot[rng.randint(0, 15, nmp)], rng.randint(0, n, nmp))
+    level = np.minimum(7, kps["octave"][tgt] + rng.randint(0, 2, nmp)).astype(np.int32)
+    radius = (th * scale[level]).astype(f32)
+    x = (kps["x"][tgt] + rng.uniform(-0.7, 0.7, nmp) * radius).astype(f32)
+    y = (kps["y"][tgt] + rng.uniform(-0.7, 0.7, nmp) * radius).astype(f32)
+    z = np.where(rng.uniform(size=nmp) < 0.05, -1.0, 1.0).astype(f32)
+    world = np.stack([x * z, y * z, z], 1).astype(f32)
+    dist = np.sqrt((world.astype(np.float64) ** 2).sum(1))
+    facing = rng.uniform(size=nmp) < 0.93
+    in_range = rng.uniform(size=nmp) < 0.93
+    mp = dict(bad=(rng.uniform(size=nmp) < 0.05).astype(np.uint8), world=world, normal=(world / dist[:, None] * np.where(facing, 1.0, -1.0)[:, None]).astype(f32),
+              min_dist=np.where(in_range, 0.0, dist * 2).astype(f32), max_dist=np.full(nmp, 1e9, f32), level=level, desc=desc[tgt].copy())
+    for i in range(nmp):
+        for b in rng.choice(256, size=int(rng.randint(0, 90)), replace=False):
+            mp["desc"][i, b >> 3] ^= np.uint8(1 << (b & 7))
+    row_state = np.where(rng.uniform(size=n) < 0.4, np.where(rng.uniform(size=n) < 0.15, -3, -2), -1).astype(np.int32)
+    found = rng.choice(nmp, 30, replace=False)
+    row_state[rng.choice(n, 30, replace=False)] = found
+    Scw = np.diag([4, 4, 4, 1]).astype(f32)
+    got_row, got_rep, rnf = Rf.fuse_sim3(kps, desc, row_state, grid, [0, W, 0, H], scale, [1, 1, 0, 0], Scw, mp, th)
+    already = set(int(v) for v in found if not mp["bad"][v])                 # GetMapPoints() leaves bad points out; they are skipped as bad anyway
+    q, qd, src = [], [], []
+    for i in range(nmp):
+        if mp["bad"][i] or i in already or z[i] < 0 or not (0 <= x[i] < W and 0 <= y[i] < H) or not in_range[i] or not facing[i]:
+            continue
+        q.append((x[i], y[i], radius[i], 0.0, level[i] - 1, level[i], PC.PQ_BEST_ONLY, 0.0)); qd.append(mp["desc"][i]); src.append(i)
+    q = np.array(q, PC.PROJ_QUERY_DTYPE)
+    pm, _, nm = O.search_by_projection(kps, desc, q, np.stack(qd), grid, th_high=50, nnratio=0.8)
+    want = np.full(nmp, -1, np.int32)
+    for k in range(len(q)):
+        if pm["accepted"][k]:
+            r = int(pm["best_idx"][k])
+            row_is_bad = row_state[r] == -3 or (row_state[r] >= 0 and mp["bad"][row_state[r]])
+            want[src[k]] = -1 if row_is_bad else r
+    assert np.array_equal(got_row, want), "%d map points differ" % int((got_row != want).sum())
+    assert rnf == int(pm["accepted"].sum()) and rnf > 100
+    assert 0 < got_rep.sum() < (got_row >= 0).sum()                           # both outcomes: replaced and added
