@@ -61,6 +61,8 @@ def lib(fma=False):
     L.ref_search_by_projection_sim3.restype = C.c_int
     L.ref_fuse_sim3.argtypes = [vp, vp, C.c_int, vp, vp, vp, vp, C.c_int, vp, vp, C.c_int, vp, vp, vp, vp, vp, vp, vp, C.c_float, vp, vp]
     L.ref_fuse_sim3.restype = C.c_int
+    L.ref_search_by_sim3.argtypes = [vp, vp, C.c_int, vp, vp, vp, vp, vp, vp] * 2 + [vp, vp, vp, vp, C.c_int, vp, C.c_float, vp, vp, C.c_float, vp]
+    L.ref_search_by_sim3.restype = C.c_int
     L.ref_kb8_project.argtypes = [vp, vp, C.c_int, vp]
     L.ref_kb8_project.restype = None
     L.ref_kb8_unproject.argtypes = [vp, vp, C.c_int, vp]
@@ -256,6 +258,24 @@ def fuse_sim3(kps, desc, row_state, grid4, bounds4, scale_factors, cam4, Scw, mp
     nf = lib().ref_fuse_sim3(_ptr(kps), _ptr(desc), len(kps), _ptr(rs), _ptr(g), _ptr(b), _ptr(sf), len(sf), _ptr(cam4), _ptr(Scw), nmp, *[_ptr(a) for a in arrs],
                              float(th), _ptr(row), _ptr(rep))
     return row[:nmp], rep[:nmp], nf
+
+
+def search_by_sim3(kf1, kf2, pre12, grid4, bounds4, scale_factors, cam4, s12, R12, t12, th):
+    """The reference's own ORBmatcher::SearchBySim3 on arrays; kf = dict(kps, desc, has_mp, bad, world, min_dist, max_dist, level).
+    Returns (match12[n1], nFound)."""
+    c = lambda a, t: np.ascontiguousarray(a, t)  # noqa: E731
+    f = np.float32
+    def side(k):
+        return [c(k["kps"], KP_DTYPE), c(k["desc"], np.uint8), None, c(k["has_mp"], np.uint8), c(k["bad"], np.uint8), c(k["world"], f), c(k["min_dist"], f),
+                c(k["max_dist"], f), c(k["level"], np.int32)]
+    a, b = side(kf1), side(kf2)
+    n1, n2 = len(a[0]), len(b[0])
+    pre, g, bd, sf, cam4, R12, t12 = c(pre12, np.int32), c(grid4, f), c(bounds4, f), c(scale_factors, f), c(cam4, f), c(np.asarray(R12, f).reshape(9), f), c(t12, f)
+    out = np.zeros(max(n1, 1), np.int32)
+    pa = [_ptr(a[0]), _ptr(a[1]), n1] + [_ptr(v) for v in a[3:]]
+    pb = [_ptr(b[0]), _ptr(b[1]), n2] + [_ptr(v) for v in b[3:]]
+    nf = lib().ref_search_by_sim3(*pa, *pb, _ptr(pre), _ptr(g), _ptr(bd), _ptr(sf), len(sf), _ptr(cam4), float(s12), _ptr(R12), _ptr(t12), float(th), _ptr(out))
+    return out[:n1], nf
 
 
 def kb8_project(cam, p3):

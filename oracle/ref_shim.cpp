@@ -133,6 +133,8 @@ public:
     cv::Mat mNormalVector;
     int predictedLevel = 0, queryIndex = -1, rowIndex = -1, fusedRow = -1, fusedHow = 0;
     bool IsInKeyFrame(KeyFrame*) { return inKF; }
+    std::tuple<int, int> GetIndexInKeyFrame(KeyFrame*) { return std::tuple<int, int>(indexInOther, -1); }   /* SearchBySim3 asks for the index in pKF2 */
+    int indexInOther = -1;
     float GetMinDistanceInvariance() { return mfMinDistance; }
     float GetMaxDistanceInvariance() { return mfMaxDistance; }
     cv::Mat GetNormal() { return mNormalVector.clone(); }
@@ -229,6 +231,7 @@ public:
     int Fuse(KeyFrame* pKF, const std::vector<MapPoint*>& vpMapPoints, const float th = 3.0, const bool bRight = false);
     int SearchByProjection(KeyFrame* pKF, cv::Mat Scw, const std::vector<MapPoint*>& vpPoints, std::vector<MapPoint*>& vpMatched, int th, float ratioHamming = 1.0);
     int Fuse(KeyFrame* pKF, cv::Mat Scw, const std::vector<MapPoint*>& vpPoints, float th, std::vector<MapPoint*>& vpReplacePoint);
+    int SearchBySim3(KeyFrame* pKF1, KeyFrame* pKF2, std::vector<MapPoint*>& vpMatches12, const float& s12, const cv::Mat& R12, const cv::Mat& t12, const float th);
     float RadiusByViewingCos(const float& viewCos);
     void ComputeThreeMaxima(std::vector<int>* histo, const int L, int& ind1, int& ind2, int& ind3);
     static const int TH_LOW;
@@ -254,6 +257,7 @@ const int ORBmatcher::HISTO_LENGTH = 30;   /* src/ORBmatcher.cc:38 */
 #include "_ref/ORBmatcher_Fuse.inc"
 #include "_ref/ORBmatcher_SearchByProjectionSim3.inc"
 #include "_ref/ORBmatcher_FuseSim3.inc"
+#include "_ref/ORBmatcher_SearchBySim3.inc"
 
 /* protected members of the extractor, for the stage-level comparisons */
 struct Probe : ORBextractor {
@@ -756,6 +760,73 @@ int ref_fuse_sim3(const orc_keypoint* kps, const uint8_t* desc, int n, const int
         fused_row[i] = repl[i] ? repl[i]->rowIndex : store[i].fusedRow;
     }
     return nFused;
+}
+
+/* ORBmatcher::SearchBySim3(pKF1, pKF2, vpMatches12, s12, R12, t12, th) (src/ORBmatcher.cc:1967-2191) on two keyframes given as arrays (identity
+ * poses: a map point's world position is its position in both cameras' frames up to the similarity).  Per keyframe k: kps / desc [n], has_mp, bad,
+ * world [n][3], min/max distance, level (PredictScale's answer in the OTHER keyframe); pre12 [n1]: -1 or the row of keyframe 2 whose map point
+ * vpMatches12[i] already holds.  match12[i] = row of keyframe 2 whose map point vpMatches12[i] holds afterwards (-1 none).  Returns nFound. */
+int ref_search_by_sim3(const orc_keypoint* kps1, const uint8_t* desc1, int n1, const uint8_t* has1, const uint8_t* bad1, const float* world1,
+                       const float* min1, const float* max1, const int32_t* level1, const orc_keypoint* kps2, const uint8_t* desc2, int n2,
+                       const uint8_t* has2, const uint8_t* bad2, const float* world2, const float* min2, const float* max2, const int32_t* level2,
+                       const int32_t* pre12, const float* grid4, const float* bounds4, const float* scale_factors, int nlevels, const float* cam4,
+                       float s12, const float* R12, const float* t12, float th, int32_t* match12) {
+    using namespace ORB_SLAM3;
+    ArenaScope scope;
+    Pinhole camera(std::vector<float>(cam4, cam4 + 4));
+    Frame::mnMinX = grid4[0]; Frame::mnMinY = grid4[1]; Frame::mfGridElementWidthInv = grid4[2]; Frame::mfGridElementHeightInv = grid4[3];
+    KeyFrame kf[2];
+    std::vector<MapPoint> pts[2];
+    const orc_keypoint* kps[2] = {kps1, kps2};
+    const uint8_t* desc[2] = {desc1, desc2};
+    const int nn[2] = {n1, n2};
+    const uint8_t* has[2] = {has1, has2};
+    const uint8_t* bad[2] = {bad1, bad2};
+    const float* world[2] = {world1, world2};
+    const float* mn[2] = {min1, min2};
+    const float* mx[2] = {max1, max2};
+    const int32_t* lvl[2] = {level1, level2};
+    const float eye[12] = {1, 0, 0, 0, 1, 0, 0, 0, 1, 0, 0, 0};
+    for (int k = 0; k < 2; k++) {
+        const int n = nn[k];
+        Frame F;
+        F.N = n; F.Nleft = -1;
+        F.mvKeysUn.resize(n);
+        if (n) std::memcpy((void*)F.mvKeysUn.data(), kps[k], sizeof(orc_keypoint) * n);
+        F.mvKeys = F.mvKeysUn;
+        F.AssignFeaturesToGrid();
+        KeyFrame& K = kf[k];
+        K.N = n; K.NLeft = -1;
+        K.mvKeys = K.mvKeysUn = F.mvKeysUn;
+        K.mDescriptors = cv::Mat(n, 32, CV_8UC1, (void*)desc[k], 32);
+        K.mvScaleFactors.assign(scale_factors, scale_factors + nlevels);
+        K.mnMinX = bounds4[0]; K.mnMaxX = bounds4[1]; K.mnMinY = bounds4[2]; K.mnMaxY = bounds4[3];
+        K.mfGridElementWidthInv = grid4[2]; K.mfGridElementHeightInv = grid4[3];
+        K.fx = cam4[0]; K.fy = cam4[1]; K.cx = cam4[2]; K.cy = cam4[3];
+        K.mGrid.assign(FRAME_GRID_COLS, std::vector<std::vector<size_t>>(FRAME_GRID_ROWS));
+        K.mGridRight = K.mGrid;
+        for (int i = 0; i < FRAME_GRID_COLS; i++)
+            for (int j = 0; j < FRAME_GRID_ROWS; j++) K.mGrid[i][j] = F.mGrid[i][j];
+        K.mpCamera = &camera;
+        K.mRcw = mat_from(eye, 3, 3); K.mtcw = mat_from(eye + 9, 3, 1);
+        { std::vector<MapPoint> fresh(n); pts[k].swap(fresh); }   /* MapPoint holds a mutex: no resize() */
+        K.mvpMapPoints.assign(n, nullptr);
+        for (int i = 0; i < n; i++) {
+            MapPoint& m = pts[k][i];
+            m.bad = bad[k][i] != 0; m.rowIndex = i;
+            m.mWorldPos = mat_from(world[k] + 3 * i, 3, 1);
+            m.mfMinDistance = mn[k][i]; m.mfMaxDistance = mx[k][i]; m.predictedLevel = lvl[k][i];
+            m.mDescriptor = cv::Mat(1, 32, CV_8UC1, (void*)(desc[k] + (size_t)i * 32), 32);   /* a map point's descriptor: its keypoint's */
+            if (has[k][i]) K.mvpMapPoints[i] = &m;
+        }
+    }
+    std::vector<MapPoint*> matches(n1, nullptr);
+    for (int i = 0; i < n1; i++)
+        if (pre12[i] >= 0) { matches[i] = &pts[1][pre12[i]]; pts[1][pre12[i]].indexInOther = pre12[i]; }
+    ORBmatcher matcher(0.75f, true);
+    const int nFound = matcher.SearchBySim3(&kf[0], &kf[1], matches, s12, mat_from(R12, 3, 3), mat_from(t12, 3, 1), th);
+    for (int i = 0; i < n1; i++) match12[i] = matches[i] ? matches[i]->rowIndex : -1;
+    return nFound;
 }
 
 /* KannalaBrandt8::project / unproject (src/CameraModels/KannalaBrandt8.cpp:25-41, 96-125) on n points */

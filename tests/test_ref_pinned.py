@@ -624,3 +624,70 @@ def test_fuse_sim3_equals_reference(seed):
     assert np.array_equal(got_row, want), "%d map points differ" % int((got_row != want).sum())
     assert rnf == int(pm["accepted"].sum()) and rnf > 100
     assert 0 < got_rep.sum() < (got_row >= 0).sum()                           # both outcomes: replaced and added
+
+
+@pytest.mark.parametrize("seed", [101, 102])
+def test_search_by_sim3_equals_reference(seed):
+    """ORBmatcher::SearchBySim3 (src/ORBmatcher.cc:1967-2191) — the reference's body, compiled — against the recipe of INTEGRATION.md 5a: one
+    ORBFE_PQ_BEST_ONLY search per direction (nothing blocks, th_high = TH_HIGH) and the mutual-agreement pass on the two best_idx arrays.
+    Identity poses and similarity, unit focal length, depth 1: the projections are exact."""
+    from orb_slam3_detailed_comments_kor_b200.synth import projection_cases as PC
+    f32 = np.float32
+    W, H = 752.0, 480.0
+    rng = np.random.RandomState(seed)
+    scale = np.array([f32(1.2) ** i for i in range(8)], f32)
+    th = f32(7.5)
+    c1 = PC.make_case(nq=1, seed=seed, n=700)
+    k1, d1 = c1["kps"], c1["desc"]
+    n1 = len(k1)
+    # keyframe 2: the same scene slightly moved, rows permuted, descriptors perturbed, some new keypoints
+    perm = rng.permutation(n1)
+    k2, d2 = k1[perm].copy(), d1[perm].copy()
+    k2["x"] = (k2["x"] + rng.uniform(-3, 3, n1)).astype(f32); k2["y"] = (k2["y"] + rng.uniform(-3, 3, n1)).astype(f32)
+    for i in range(n1):
+        for b in rng.choice(256, size=int(rng.randint(0, 60)), replace=False):
+            d2[i, b >> 3] ^= np.uint8(1 << (b & 7))
+    grid = c1["grid"]
+
+    def keyframe(k, d):
+        n = len(k)
+        z = np.where(rng.uniform(size=n) < 0.04, -1.0, 1.0).astype(f32)
+        world = np.stack([k["x"] * z, k["y"] * z, z], 1).astype(f32)
+        dist = np.sqrt((world.astype(np.float64) ** 2).sum(1))
+        in_range = rng.uniform(size=n) < 0.95
+        return dict(kps=k, desc=d, has_mp=(rng.uniform(size=n) < 0.8).astype(np.uint8), bad=(rng.uniform(size=n) < 0.05).astype(np.uint8), world=world,
+                    min_dist=np.where(in_range, 0.0, dist * 2).astype(f32), max_dist=np.full(n, 1e9, f32),
+                    level=np.minimum(7, k["octave"] + rng.randint(0, 2, n)).astype(np.int32), z=z, in_range=in_range)
+    kf1, kf2 = keyframe(k1, d1), keyframe(k2, d2)
+    pre12 = np.full(n1, -1, np.int32)
+    pre_rows = rng.choice(n1, 40, replace=False)
+    pre12[pre_rows] = rng.choice(n1, 40, replace=False)
+    got, rnf = Rf.search_by_sim3(kf1, kf2, pre12, grid, [0, W, 0, H], scale, [1, 1, 0, 0], 1.0, np.eye(3), np.zeros(3), th)
+
+    def one_way(src, dst, matched_src):
+        """best keypoint of dst for every map point of src (-1 none): the :2017-2091 / :2097-2171 loops as one best-only search"""
+        q, qd, rows = [], [], []
+        for i in range(len(src["kps"])):
+            if not src["has_mp"][i] or matched_src[i] or src["bad"][i] or src["z"][i] < 0 or not src["in_range"][i]:
+                continue
+            x, y = src["kps"]["x"][i], src["kps"]["y"][i]
+            if not (0 <= x < W and 0 <= y < H):
+                continue
+            lv = int(src["level"][i])
+            q.append((x, y, th * scale[lv], 0.0, lv - 1, lv, PC.PQ_BEST_ONLY, 0.0)); qd.append(src["desc"][i]); rows.append(i)
+        best = np.full(len(src["kps"]), -1, np.int32)
+        pm, _, _ = O.search_by_projection(dst["kps"], dst["desc"], np.array(q, PC.PROJ_QUERY_DTYPE), np.stack(qd), grid, th_high=100, nnratio=0.75)
+        for k, i in enumerate(rows):
+            if pm["accepted"][k]:
+                best[i] = pm["best_idx"][k]
+        return best
+    matched1 = pre12 >= 0
+    matched2 = np.zeros(n1, bool); matched2[pre12[pre12 >= 0]] = True
+    b12, b21 = one_way(kf1, kf2, matched1), one_way(kf2, kf1, matched2)
+    want = pre12.copy()
+    nfound = 0
+    for i1 in range(n1):
+        if b12[i1] >= 0 and b21[b12[i1]] == i1:
+            want[i1] = b12[i1]; nfound += 1
+    assert np.array_equal(got, want), "%d rows differ" % int((got != want).sum())
+    assert rnf == nfound and nfound > 100
