@@ -5,8 +5,10 @@
  *   /root/reference/Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1217-1260   transform(feature, word_id, weight, nid, levelsup)
  *   /root/reference/Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1338-1426   loadFromTextFile (node / word numbering)
  *   /root/reference/Thirdparty/DBoW2/DBoW2/BowVector.cpp:34-84, FeatureVector.cpp:31-45, FORB.cpp:81-101, ScoringObject.h:73-90
- * The vocabulary file (Vocabulary/ORBvoc.txt) is not in /root/reference, so the tests run on synthetic trees; parity unpinned
- * beyond the independent Python restatement in tests/test_bow.py. */
+ * The vocabulary file (Vocabulary/ORBvoc.txt) is not in /root/reference, so the tests run on synthetic trees.  PINNED: the transform against
+ * the reference's vendored DBoW2 compiled into oracle/_ref/libdbow_ref.so (bit-identical doubles), SearchByBoW x2 and SearchForTriangulation
+ * against the reference's own bodies compiled into oracle/_ref/liborb_ref.so (tests/test_ref_pinned.py, tests/test_ref_triangulation.py);
+ * an independent Python restatement in tests/test_bow.py besides. */
 #include <cmath>
 #include <cstdint>
 #include <cstring>

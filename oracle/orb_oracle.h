@@ -9,10 +9,11 @@
  * `find_package(OpenCV 4.0)`; the arithmetic restated here is pinned against cv2 4.13.0 by
  * tools/make_goldens.py -> tests/golden/, see tests/test_oracle_golden.py).
  *
- * Parity is PINNED twice: the OpenCV primitives against the real cv2 4.13 (above), and the extractor and
- * the stereo matcher as a whole against the reference's own ORBextractor.cc / Frame::ComputeStereoMatches
- * compiled in this container (oracle/Makefile -> oracle/_ref/liborb_ref.so, tests/test_ref_pinned.py):
- * identical keypoints, angles, descriptors, pyramids, uRight and depth on every golden case.
+ * Parity is PINNED twice: the OpenCV primitives against the real cv2 4.13 (above), and the extractor, the
+ * stereo matcher, every matcher function of the path and the camera-model members they call against the
+ * reference's own sources compiled in this container (oracle/Makefile -> oracle/_ref/liborb_ref.so;
+ * tests/test_ref_pinned.py, test_ref_triangulation.py, test_initialization.py): identical keypoints, angles,
+ * descriptors, pyramids, uRight and depth on every golden case, identical matches on every search.
  *
  * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may
  * load this library.  The product (liborbfe.so) never links, imports or calls it.
