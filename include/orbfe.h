@@ -281,6 +281,12 @@ int orbfe_fisheye_triangulate_batch_device(orbfe_extractor* exL, orbfe_extractor
 int orbfe_fisheye_frames_submit(orbfe_extractor* exL, orbfe_extractor* exR, const uint8_t* h_left, const uint8_t* h_right, int nframes, int lap0, int lap1,
                                 const orbfe_fisheye_rig* rig, double ratio, orbfe_keypoint* kps_l, uint8_t* desc_l, orbfe_keypoint* kps_r, uint8_t* desc_r, int cap,
                                 int32_t* match_lr, int32_t* match_rl, float* depth, float* p3d);
+/* Replaces Frame::ComputeStereoFishEyeMatches (src/Frame.cc:1119-1159) as a whole for the frames both extractors processed last (the single
+ * frame of the two operator() calls, or a batch), results on the host: match_lr [nframes*cap] = mvLeftToRightMatch (right rows), match_rl =
+ * mvRightToLeftMatch, depth = mvDepth (-1: none), p3d [nframes*cap*3] = mvStereo3Dpoints; entries beyond a frame's keypoint counts are
+ * unspecified; any output may be NULL.  ratio = 0.7 in the reference.  Synchronous. */
+int orbfe_fisheye_stereo_frames(orbfe_extractor* exL, orbfe_extractor* exR, int nframes, const orbfe_fisheye_rig* rig, double ratio, int32_t* match_lr,
+                                int32_t* match_rl, float* depth, float* p3d, int cap);
 int orbfe_kb8_triangulate_pairs_device(int device, const orbfe_fisheye_rig* rig, const float* d_uv1, const float* d_uv2, const float* d_sigma1,
                                        const float* d_sigma2, int n, float* d_depth, float* d_p3d, void* stream);
 

@@ -12,6 +12,8 @@
 #ifndef ORBFE_SHIM_MATCHING_H
 #define ORBFE_SHIM_MATCHING_H
 
+#include <algorithm>
+#include <cstring>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -72,6 +74,38 @@ inline void FishEyeKnnMatches(const cv::Mat& stereoDescLeft, const cv::Mat& ster
     for (int i = 0; i < stereoDescRight.rows; i++) std::memcpy(&t[(size_t)i * 32], stereoDescRight.ptr<unsigned char>(i), 32);
     if (orbfe_knn2_ratio(device, q.data(), stereoDescLeft.rows, t.data(), stereoDescRight.rows, 0.7, match.data(), nullptr, nullptr) != ORBFE_OK)
         throw std::runtime_error(std::string("orbfe_knn2_ratio: ") + orbfe_last_error());
+}
+
+/* Body of Frame::ComputeStereoFishEyeMatches (src/Frame.cc:1119-1159) as a whole, for the frame the two extractors have just processed with
+ * the lapping interval: knnMatch(k=2) + `d0 < d1*0.7`, KannalaBrandt8::TriangulateMatches per survivor, `depth > 0.0001f`.
+ *   cam1 / cam2: mpCamera->mvParameters / mpCamera2->mvParameters (fx, fy, cx, cy, k0..k3); Rlr row-major 3x3 and tlr: mRlr, mtlr.
+ * Inside the member the body becomes
+ *     ORB_SLAM3::orbfe::ComputeStereoFishEyeMatches(mpORBextractorLeft, mpORBextractorRight, Nleft, Nright, cam1, cam2, Rlr, tlr,
+ *                                                   mvLeftToRightMatch, mvRightToLeftMatch, mvDepth, mvStereo3Dpoints);
+ * mvStereo3Dpoints receives x, y, z per left keypoint (the reference stores cv::Mat; the caller wraps the triple). */
+inline void ComputeStereoFishEyeMatches(ORBextractor* left, ORBextractor* right, int Nleft, int Nright, const float cam1[8], const float cam2[8], const float Rlr[9],
+                                        const float tlr[3], std::vector<int>& mvLeftToRightMatch, std::vector<int>& mvRightToLeftMatch,
+                                        std::vector<float>& mvDepth, std::vector<float>& mvStereo3Dpoints) {
+    mvLeftToRightMatch.assign(Nleft, -1);
+    mvRightToLeftMatch.assign(Nright, -1);
+    mvDepth.assign(Nleft, -1.0f);
+    mvStereo3Dpoints.assign((size_t)Nleft * 3, 0.0f);
+    if (Nleft == 0 || Nright == 0) return;
+    orbfe_fisheye_rig rig;
+    std::memcpy(rig.cam1, cam1, sizeof rig.cam1); std::memcpy(rig.cam2, cam2, sizeof rig.cam2);
+    std::memcpy(rig.R12, Rlr, sizeof rig.R12); std::memcpy(rig.t12, tlr, sizeof rig.t12);
+    const int cap = orbfe_keypoint_capacity(left->Impl());
+    std::vector<int> lr(cap), rl(cap);
+    std::vector<float> d(cap), p((size_t)cap * 3);
+    if (orbfe_fisheye_stereo_frames(left->Impl(), right->Impl(), 1, &rig, 0.7, lr.data(), rl.data(), d.data(), p.data(), cap) != ORBFE_OK)
+        throw std::runtime_error(std::string("orbfe_fisheye_stereo_frames: ") + orbfe_last_error());
+    std::copy(lr.begin(), lr.begin() + Nleft, mvLeftToRightMatch.begin());
+    std::copy(rl.begin(), rl.begin() + Nright, mvRightToLeftMatch.begin());
+    for (int i = 0; i < Nleft; i++) {
+        if (lr[i] < 0) continue;
+        mvDepth[i] = d[i];
+        for (int k = 0; k < 3; k++) mvStereo3Dpoints[(size_t)i * 3 + k] = p[(size_t)i * 3 + k];
+    }
 }
 
 /* The loop of ORBmatcher::SearchByProjection(Frame &F, const vector<MapPoint*> &vpMapPoints, th, bFarPoints, thFarPoints)

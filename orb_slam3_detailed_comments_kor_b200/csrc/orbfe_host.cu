@@ -659,6 +659,43 @@ int orbfe_extract_batch_host(orbfe_extractor* ex, const uint8_t* h_images, int n
 /* One batch of stereo pairs through upload -> both extractions -> stereo matching -> download, enqueued chunk by chunk and not
  * waited for.  `slot` (0/1) selects the input staging buffers and the pinned count arrays, so that the upload of one batch can
  * run while the previous batch is still in the kernels. */
+/* device buffers of the fisheye-rig stereo outputs (match vectors and 3-D points; the depths share b.depth): allocated on first use */
+static int fisheye_buffers(orbfe_extractor* exL) {
+    if (exL->fishLR) return ORBFE_OK;
+    const size_t n = (size_t)exL->maxBatch * exL->d.kpCap;
+    ORBFE_CUDA(cudaMalloc((void**)&exL->fishLR, n * sizeof(int32_t))); exL->allocs.push_back(exL->fishLR);
+    ORBFE_CUDA(cudaMalloc((void**)&exL->fishRL, n * sizeof(int32_t))); exL->allocs.push_back(exL->fishRL);
+    ORBFE_CUDA(cudaMalloc((void**)&exL->fishP3d, n * 3 * sizeof(float))); exL->allocs.push_back(exL->fishP3d);
+    return ORBFE_OK;
+}
+
+/* Frame::ComputeStereoFishEyeMatches (src/Frame.cc:1119-1159) for the frames both extractors processed last, results on the host:
+ * knn-2 + ratio, TriangulateMatches, the depth test.  match_lr / depth: per frame `cap` entries of which the first n_left are written,
+ * match_rl: the first n_right, p3d: 3 * n_left (cap >= the keypoint capacity).  Synchronous. */
+extern "C" int orbfe_fisheye_stereo_frames(orbfe_extractor* exL, orbfe_extractor* exR, int nframes, const orbfe_fisheye_rig* rig, double ratio, int32_t* match_lr,
+                                           int32_t* match_rl, float* depth, float* p3d, int cap) {
+    if (!exL || !exR || !rig) { orbfe_set_error("null argument"); return ORBFE_E_INVALID; }
+    if (exL == exR || exL->device != exR->device || exL->d.kpCap != exR->d.kpCap) { orbfe_set_error("left/right extractors must be two objects of the same geometry on one device"); return ORBFE_E_INVALID; }
+    if (nframes < 1 || nframes > exL->lastBatch || nframes > exR->lastBatch) { orbfe_set_error("nframes exceeds the last extracted batch"); return ORBFE_E_INVALID; }
+    if (cap < exL->d.kpCap) { orbfe_set_error("cap %d < keypoint capacity %d", cap, exL->d.kpCap); return ORBFE_E_CAPACITY; }
+    if (exL->pendingCount) { orbfe_set_error("batches submitted with orbfe_stereo_frames_submit are still in flight"); return ORBFE_E_INVALID; }
+    ORBFE_CUDA(cudaSetDevice(exL->device));
+    { int rc = fisheye_buffers(exL); if (rc) return rc; }
+    { int rc = orbfe_wait_last(exL); if (!rc) rc = orbfe_wait_last(exR); if (rc) return rc; }
+    cudaStream_t st = exL->stream;
+    const int kc = exL->d.kpCap;
+    int rc = orbfe_launch_fisheye(exL, exR, nframes, 0, ratio, rig, exL->fishLR, exL->fishRL, exL->b.depth, exL->fishP3d, st);
+    if (rc) return rc;
+    const size_t w = (size_t)kc * 4;
+    if (match_lr) ORBFE_CUDA(cudaMemcpy2DAsync(match_lr, (size_t)cap * 4, exL->fishLR, w, w, nframes, cudaMemcpyDeviceToHost, st));
+    if (match_rl) ORBFE_CUDA(cudaMemcpy2DAsync(match_rl, (size_t)cap * 4, exL->fishRL, w, w, nframes, cudaMemcpyDeviceToHost, st));
+    if (depth) ORBFE_CUDA(cudaMemcpy2DAsync(depth, (size_t)cap * 4, exL->b.depth, w, w, nframes, cudaMemcpyDeviceToHost, st));
+    if (p3d) ORBFE_CUDA(cudaMemcpy2DAsync(p3d, (size_t)cap * 12, exL->fishP3d, 3 * w, 3 * w, nframes, cudaMemcpyDeviceToHost, st));
+    ORBFE_CUDA(cudaStreamSynchronize(st));
+    rc = orbfe_mark_last(exL, st);
+    return rc ? rc : orbfe_mark_last(exR, st);
+}
+
 struct FishArgs {   /* the fisheye-rig variant of the batch: ComputeStereoFishEyeMatches instead of ComputeStereoMatches */
     const orbfe_fisheye_rig* rig;
     double ratio;
@@ -670,12 +707,7 @@ static int stereo_frames_enqueue(orbfe_extractor* exL, orbfe_extractor* exR, con
                                  float mbf, float min_d, float max_d, orbfe_keypoint* kps_l, uint8_t* desc_l, orbfe_keypoint* kps_r, uint8_t* desc_r, int cap,
                                  float* u_right, float* depth, int slot, int chunk, const FishArgs* fish) {
     const int kc = exL->d.kpCap;
-    if (fish && !exL->fishLR) {
-        const size_t n = (size_t)exL->maxBatch * kc;
-        ORBFE_CUDA(cudaMalloc((void**)&exL->fishLR, n * sizeof(int32_t))); exL->allocs.push_back(exL->fishLR);
-        ORBFE_CUDA(cudaMalloc((void**)&exL->fishRL, n * sizeof(int32_t))); exL->allocs.push_back(exL->fishRL);
-        ORBFE_CUDA(cudaMalloc((void**)&exL->fishP3d, n * 3 * sizeof(float))); exL->allocs.push_back(exL->fishP3d);
-    }
+    if (fish) { const int rc = fisheye_buffers(exL); if (rc) return rc; }
     const size_t frameBytes = (size_t)exL->d.W * exL->d.H;
     exL->lastBatch = exR->lastBatch = nframes;
     cudaStream_t sl = exL->stream, sr = exR->stream, in = exL->copyIn, out = exL->copyOut;

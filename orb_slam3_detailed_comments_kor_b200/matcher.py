@@ -136,6 +136,17 @@ def stereo_frames_submit(exL, exR, left, right, mbf, minD, maxD, vLappingArea, o
                                                 C.c_float(mbf), C.c_float(minD), C.c_float(maxD), ptr(kl), ptr(dl), ptr(kr), ptr(dr), cap, ptr(u), ptr(d)))
 
 
+def fisheye_stereo_frames(exL, exR, nframes, rig, ratio=0.7):
+    """Frame::ComputeStereoFishEyeMatches for the frames both extractors processed last; returns host arrays
+    (match_lr[n, cap], match_rl[n, cap], depth[n, cap], p3d[n, cap, 3])."""
+    cap = exL.capacity
+    lr, rl = np.full((nframes, cap), -1, np.int32), np.full((nframes, cap), -1, np.int32)
+    d, p3 = np.full((nframes, cap), -1, np.float32), np.zeros((nframes, cap, 3), np.float32)
+    rig = np.ascontiguousarray(rig, np.float32)
+    check(_lib.lib().orbfe_fisheye_stereo_frames(exL.handle, exR.handle, nframes, ptr(rig), C.c_double(ratio), ptr(lr), ptr(rl), ptr(d), ptr(p3), cap))
+    return lr, rl, d, p3
+
+
 def fisheye_frames_submit(exL, exR, left, right, rig, ratio, vLappingArea, out):
     """orbfe_fisheye_frames_submit: like stereo_frames_submit for a fisheye rig.  `out` = (cntL, monoL, kpsL, descL, cntR, monoR, kpsR,
     descR, match_lr[n, cap] i32, match_rl[n, cap] i32, depth[n, cap] f32, p3d[n, cap, 3] f32); collect with fisheye_frames_wait."""

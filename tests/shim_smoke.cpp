@@ -98,10 +98,31 @@ int main(int argc, char** argv) {
     const int ini = orbfe::SearchForInitialization(kL, dL, kR, dR, 0.f, 0.f, 64.f / W, 48.f / H, prevMatched, ini12, 100, 0.9f, true, ORBmatcher::TH_LOW);
     int iniCount = 0;
     for (int v : ini12) iniCount += v >= 0;
+    // a fisheye rig: both images with the lapping interval, then the whole Frame::ComputeStereoFishEyeMatches (src/Frame.cc:1119-1159)
+    int fishMatches = 0;
+    long fishSum = 0;
+    {
+        const int FW = 512, FH = 512;
+        cv::Mat fL(FH, FW, CV_8UC1), fR(FH, FW, CV_8UC1);
+        orbfe_synth_stereo(800, FW, FH, fL.ptr<unsigned char>(0), fR.ptr<unsigned char>(0));
+        ORBextractor exl(1500, 1.2f, 8, 20, 7), exr(1500, 1.2f, 8, 20, 7);
+        std::vector<cv::KeyPoint> fkL, fkR;
+        cv::Mat fdL, fdR;
+        std::vector<int> flap = {0, 511};
+        exl(fL, mask, fkL, fdL, flap);
+        exr(fR, mask, fkR, fdR, flap);
+        const float cam[8] = {190.f, 190.f, 256.f, 256.f, 0.f, 0.f, 0.f, 0.f};
+        const float Rlr[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1}, tlr[3] = {0.1f, 0.f, 0.f};
+        std::vector<int> l2r, r2l;
+        std::vector<float> fdepth, fp3d;
+        orbfe::ComputeStereoFishEyeMatches(&exl, &exr, (int)fkL.size(), (int)fkR.size(), cam, cam, Rlr, tlr, l2r, r2l, fdepth, fp3d);
+        for (size_t i = 0; i < l2r.size(); i++)
+            if (l2r[i] >= 0) { fishMatches++; fishSum += (long)(i + 1) * (l2r[i] + 1); }
+    }
     cv::Mat empty;
     const int rcEmpty = left(empty, mask, kR, dR, lap);
-    printf("shim n=%zu mono=%d monoR=%d levels=%d pyr0=%dx%d stereo=%d d01=%d top2acc=%d proj=%d projself=%d init=%d initcount=%d empty=%d first=(%.1f,%.1f,%.3f,%d)\n",
-           kL.size(), monoL, monoR, left.GetLevels(), left.mvImagePyramid[0].cols, left.mvImagePyramid[0].rows, matched, d01, acc, proj, projSelf, ini, iniCount, rcEmpty,
+    printf("shim n=%zu mono=%d monoR=%d levels=%d pyr0=%dx%d stereo=%d d01=%d top2acc=%d proj=%d projself=%d init=%d initcount=%d fish=%d fishsum=%ld empty=%d first=(%.1f,%.1f,%.3f,%d)\n",
+           kL.size(), monoL, monoR, left.GetLevels(), left.mvImagePyramid[0].cols, left.mvImagePyramid[0].rows, matched, d01, acc, proj, projSelf, ini, iniCount, fishMatches, fishSum, rcEmpty,
            kL[0].pt.x, kL[0].pt.y, kL[0].angle, kL[0].octave);
     return 0;
 }

@@ -71,5 +71,21 @@ def test_shim_matches_oracle(tmp_path):
     assert nm > 1000
     im, _, inm = O.search_for_initialization(kL, dL, kR, dR, grid, np.stack([kL["x"], kL["y"]], 1), 100, 0.9, True)
     assert int(f["init"]) == inm and int(f["initcount"]) == int((im >= 0).sum()) and inm > 10
+    # the fisheye rig of the probe: extraction with the lapping interval, knn-2 + 0.7, TriangulateMatches, depth test (src/Frame.cc:1119-1159)
+    fL, fR = synth.stereo_pair(800, 512, 512)
+    fp = (1500, 1.2, 8, 20, 7)
+    xl, xr = O.OracleExtractor(*fp), O.OracleExtractor(*fp)
+    ml, fkl, fdl = xl(fL, (0, 511)); mr, fkr, fdr = xr(fR, (0, 511))
+    knn = O.knn2_ratio(fdl[ml:], fdr[mr:], 0.7)
+    knn = knn[0] if isinstance(knn, tuple) else knn
+    sig = np.asarray(xl.scale_factors(), np.float32) ** 2
+    cam = np.array([190, 190, 256, 256, 0, 0, 0, 0], np.float32)
+    qi = np.nonzero(knn >= 0)[0]
+    li, ri = qi + ml, knn[qi] + mr
+    dep, _ = O.kb8_triangulate_matches(cam, cam, np.eye(3, dtype=np.float32), np.array([0.1, 0, 0], np.float32), np.stack([fkl["x"][li], fkl["y"][li]], 1),
+                                       np.stack([fkr["x"][ri], fkr["y"][ri]], 1), sig[fkl["octave"][li]], sig[fkr["octave"][ri]])
+    keep = dep > 0.0001
+    assert int(f["fish"]) == int(keep.sum()) and int(f["fishsum"]) == int(((li[keep] + 1).astype(np.int64) * (ri[keep] + 1)).sum())
+    assert keep.sum() >= 3
     first = "(%.1f,%.1f,%.3f,%d)" % (kL[0]["x"], kL[0]["y"], kL[0]["angle"], kL[0]["octave"])
     assert f["first"] == first

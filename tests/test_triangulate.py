@@ -148,6 +148,12 @@ def test_gpu_fisheye_stereo_frame_on_device():
             assert np.max(np.abs(p3d[f, :cl[f]][ok] - wp_full[ok]) / np.abs(wp_full[ok]).max(1, keepdims=True)) <= REL_TOL
         kept += int(ok.sum())
     assert kept > 10, kept
+    # the host-output call for the same frames (what the C++ shim's ComputeStereoFishEyeMatches uses)
+    h_lr, h_rl, h_d, h_p = M.fisheye_stereo_frames(exL, exR, nb, M.make_fisheye_rig(cam, cam, R12, t12), 0.7)
+    for f in range(nb):
+        assert np.array_equal(h_lr[f, :cl[f]], lr[f, :cl[f]]) and np.array_equal(h_rl[f, :cr[f]], rl[f, :cr[f]])
+        ok = lr[f, :cl[f]] >= 0
+        assert np.array_equal(h_d[f, :cl[f]][ok], depth[f, :cl[f]][ok]) and np.array_equal(h_p[f, :cl[f]][ok], p3d[f, :cl[f]][ok])
     exL.close(); exR.close()
 
 
