@@ -1009,6 +1009,54 @@ def main():
            "words_in_frame0": int(len(voc.result(0, int(exL.batch_counts(1)[0][0]))["bow_words"])),
            "note": "Frame::ComputeBoW = DBoW2 transform(features, BowVec, FeatVec, 4); extractor buffers chained on the device"}
 
+    # ---- the consumers of the feature vectors: SearchByBoW and SearchForTriangulation between consecutive frames of the
+    #      batch, chained on the device behind the transform above; and MapPoint::ComputeDistinctiveDescriptors (N4) for 20000 map points
+    bv = [C.c_void_p() for _ in range(9)]
+    _lib.check(L.orbfe_bow_device_views(voc.handle, *[C.byref(v) for v in bv]))
+    NP = P - 1
+    d_pk, d_pf = torch.arange(0, NP, dtype=torch.int32, device="cuda"), torch.arange(1, P, dtype=torch.int32, device="cuda")
+    d_sm, d_snm = torch.zeros((NP, exL.capacity), dtype=torch.int32, device="cuda"), torch.zeros(NP, dtype=torch.int32, device="cuda")
+    Kc = np.array([[458.654, 0, 367.215], [0, 457.296, 248.375], [0, 0, 1]], np.float64)
+    F12 = (np.linalg.inv(Kc).T @ np.array([[0, 0, 0], [0, 0, -0.11], [0, 0.11, 0]]) @ np.linalg.inv(Kc)).astype(np.float32)
+    sf16 = np.array([np.float32(1.2) ** i for i in range(16)], np.float32)
+    d_f12, d_ep = to_dev(np.tile(F12.reshape(9), NP)), to_dev(np.tile(np.array([-3000.0, 240.0], np.float32), NP))
+    d_sf, d_sig = to_dev(sf16), to_dev((sf16 * sf16).astype(np.float32))
+
+    def sbb_step():
+        _lib.check(L.orbfe_search_by_bow_device(local_rank, NP, exL.capacity, d_pk.data_ptr(), d_pf.data_ptr(), vd.value, vk.value, exL.capacity, bv[5].value,
+                                                bv[6].value, bv[7].value, bv[8].value, None, None, 50, C.c_float(0.7), 1, 0, d_sm.data_ptr(), None,
+                                                d_snm.data_ptr(), st))
+
+    def sft_step():
+        _lib.check(L.orbfe_search_for_triangulation_device(local_rank, NP, exL.capacity, d_pk.data_ptr(), d_pf.data_ptr(), vd.value, vk.value, None, exL.capacity,
+                                                           bv[5].value, bv[6].value, bv[7].value, bv[8].value, None, d_f12.data_ptr(), d_ep.data_ptr(),
+                                                           d_sf.data_ptr(), d_sig.data_ptr(), 50, 0, 0, 1, d_sm.data_ptr(), d_snm.data_ptr(), st, None))
+    drng = np.random.RandomState(5)
+    dd_off = np.concatenate([[0], np.cumsum(drng.randint(2, 16, 20000))]).astype(np.int32)
+    dd_desc = drng.randint(0, 256, (int(dd_off[-1]), 32)).astype(np.uint8)
+    d_dd, d_doff = to_dev(dd_desc), to_dev(dd_off)
+    d_didx, d_dmed = torch.zeros(20000, dtype=torch.int32, device="cuda"), torch.zeros(20000, dtype=torch.int32, device="cuda")
+
+    def dd_step():
+        _lib.check(L.orbfe_distinctive_descriptors_device(local_rank, d_dd.data_ptr(), d_doff.data_ptr(), 20000, d_didx.data_ptr(), d_dmed.data_ptr(), st))
+    consumers = {}
+    for name, fn, units, unit in (("search_by_bow", sbb_step, NP, "frame_pairs/s"), ("search_for_triangulation", sft_step, NP, "keyframe_pairs/s"),
+                                  ("distinctive_descriptors", dd_step, 20000, "map_points/s")):
+        for _ in range(3):
+            fn()
+        barrier()
+        e0.record()
+        for _ in range(args.steps):
+            fn()
+        e1.record()
+        barrier()
+        ms = max_over_ranks(e0.elapsed_time(e1) / args.steps)
+        consumers[name] = {"value": units * world / (ms / 1e3), "unit": unit, "ms_per_step": ms, "per_step": units * world}
+    consumers["search_by_bow"]["note"] = "ORBmatcher::SearchByBoW(pKF, F, ...) between consecutive frames of the batch, feature vectors from the transform above (device chain)"
+    consumers["search_by_bow"]["matches_per_pair"] = float(d_snm.float().mean().item())
+    consumers["search_for_triangulation"]["note"] = "ORBmatcher::SearchForTriangulation (pinhole, Pinhole::epipolarConstrain on a sideways F12) on the same pairs"
+    consumers["distinctive_descriptors"]["note"] = "MapPoint::ComputeDistinctiveDescriptors, 2-15 observations per map point"
+
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cores = os.cpu_count() or 1
@@ -1038,13 +1086,28 @@ def main():
             list(tp.map(pj_cpu, range(reps)))
         pdt = time.perf_counter() - t0
         ovoc = O.OracleVocabulary(10, 6, 0, 0, v_parent, v_leaf, v_desc, v_weight)
-        cntL0, _, _, descL0 = exL.extract_batch_host(hLn[:8], (0, 0))
+        cntL0, _, kpsL0, descL0 = exL.extract_batch_host(hLn[:8], (0, 0))
         bsample = [np.ascontiguousarray(descL0[i, :cntL0[i]]) for i in range(8)]
+        ksample = [np.ascontiguousarray(kpsL0[i, :cntL0[i]]) for i in range(8)]
         t0 = time.perf_counter()
         with ThreadPoolExecutor(cores) as tp:
             list(tp.map(lambda i: ovoc.transform(bsample[i % 8], 4), range(8 * cores)))
         bdt = time.perf_counter() - t0
         cpu["bow"] = {"value": 8 * cores / bdt, "unit": "frames/s", "sample": "%d frames (%.2f s wall) frame-parallel over %d threads" % (8 * cores, bdt, cores)}
+        fvs = [ovoc.transform(bsample[i], 4)["feat_vec"] for i in range(8)]
+        scale8 = sf16[:8].copy()
+        for name, call in (("search_by_bow", lambda i: O.search_by_bow(bsample[i % 7], ksample[i % 7], fvs[i % 7], None, bsample[i % 7 + 1], ksample[i % 7 + 1], fvs[i % 7 + 1], 50, 0.7, True)),
+                           ("search_for_triangulation", lambda i: O.search_for_triangulation(bsample[i % 7], ksample[i % 7], None, None, fvs[i % 7], bsample[i % 7 + 1], ksample[i % 7 + 1], None,
+                                                                                             None, fvs[i % 7 + 1], F12, [-3000.0, 240.0], scale8, scale8 * scale8, 50, False, False, True))):
+            t0 = time.perf_counter()
+            with ThreadPoolExecutor(cores) as tp:
+                list(tp.map(call, range(8 * cores)))
+            cdt = time.perf_counter() - t0
+            cpu[name] = {"value": 8 * cores / cdt, "unit": consumers[name]["unit"], "kind": "port", "sample": "%d pairs (%.2f s wall) pair-parallel over %d threads" % (8 * cores, cdt, cores)}
+        t0 = time.perf_counter()
+        O.distinctive_descriptors(dd_desc[:int(dd_off[4000])], dd_off[:4001])
+        cdt = time.perf_counter() - t0
+        cpu["distinctive_descriptors"] = {"value": 4000 / cdt, "unit": "map_points/s", "kind": "port", "sample": "4000 map points (%.2f s wall), one thread" % cdt}
         from oracle import ref_oracle as _RO
         init_fn = _RO.search_for_initialization if reference_available() else O.search_for_initialization
         t0 = time.perf_counter()
@@ -1067,7 +1130,7 @@ def main():
                                        "ExtractORB threads), blur beside quadtree + assemble, ComputeStereoMatches behind both; timed by events on the caller's stream",
                            "serial_ms_per_step": ms_serial},
                 "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
-                "single_frame_latency_ms": single_ms, "shim_single_frame_latency_ms": shim_ms, "rectify": rectify, "projection": projection, "initialization": initialization, "bow": bow,
+                "single_frame_latency_ms": single_ms, "shim_single_frame_latency_ms": shim_ms, "rectify": rectify, "projection": projection, "initialization": initialization, "bow": bow, "consumers": consumers,
                 "gpu_launches": (2 * (PARAMS[2] + 8) + 3) * args.steps,
                 "hamming": hamming}
         print(json.dumps(line), flush=True)

@@ -202,13 +202,16 @@ __global__ void __launch_bounds__(BOW_NT) k_bow_assemble(const int* __restrict__
  * (ComputeThreeMaxima) removes the matches outside the three fullest bins.
  * One CTA = one (keyframe, frame) pair.  The serial "already matched" rule is reproduced exactly by the speculative rounds of
  * orbfe_project.cu: a query (one keyframe feature, in feature-vector order) stamps the unmatched frame features of its node,
- * scans them, and becomes final iff no candidate at or below its second-best distance carries the stamp of an earlier unresolved
- * query.  Queries of different nodes never share a candidate, so everything but the chains inside a node resolves at once. */
+ * that it could take (distance <= TH_LOW), scans them, and becomes final iff no candidate at or below its second-best distance carries
+ * the stamp of an earlier unresolved query.  Queries of different nodes never share a candidate, and inside a node only queries that
+ * compete for a feature both could take wait for each other. */
 #define SB_NT 256
+#define SB_FREE 0xFFFFu      /* takenBy: nobody */
+#define SB_PENDING 0x8000u   /* takenBy: taken in the running round, visible from the next one */
 struct SbSmem {
     int owner[BOW_MAXF];
     uint32_t range[BOW_MAXF];          /* per query: first | last+1 << 16 of its node's run in the frame's fvFeats (0 = none) */
-    uint32_t taken[BOW_MAXF / 4];      /* per frame feature: bit 0 matched, bit 1 matched as of the next round */
+    uint16_t takenBy[BOW_MAXF];        /* per frame feature: 1 + the query that took it (0: occupied before the search), SB_FREE, | SB_PENDING */
     uint32_t state[BOW_MAXF / 4];      /* per query: 0 unresolved, 1 resolved */
     int rot[32];
 };
@@ -230,13 +233,12 @@ __global__ void __launch_bounds__(SB_NT) k_search_by_bow(int maxF, const int* __
     const uint4* descA = desc + (size_t)a * rowStride * 2; const uint4* descB = desc + (size_t)b * rowStride * 2;
     int* mF = matchF + (size_t)pr * rowStride;
     orbfe_match* ko = kfOut ? kfOut + (size_t)pr * rowStride : nullptr;
-    uint8_t* takenB = reinterpret_cast<uint8_t*>(s.taken);
     uint8_t* stateB = reinterpret_cast<uint8_t*>(s.state);
     for (int i = tid; i < rowStride; i += SB_NT) { mF[i] = -1; if (ko) { orbfe_match m; m.best1 = 256; m.best2 = 256; m.idx = -1; m.accepted = 0; ko[i] = m; } }
-    for (int i = tid; i < BOW_MAXF / 4; i += SB_NT) { s.taken[i] = 0; s.state[i] = 0; }
+    for (int i = tid; i < BOW_MAXF / 4; i += SB_NT) s.state[i] = 0;
+    /* keyframe-keyframe variant: rows of the second keyframe without a map point are never candidates (:886-892) */
+    for (int i = tid; i < BOW_MAXF; i += SB_NT) s.takenBy[i] = (kfkf && hasMp && i < rowStride && !hasMp[(size_t)b * rowStride + i]) ? 0 : SB_FREE;
     __syncthreads();
-    if (kfkf && hasMp)   /* keyframe-keyframe variant: rows of the second keyframe without a map point are never candidates (:886-892) */
-        for (int i = tid; i < min(rowStride, BOW_MAXF); i += SB_NT) takenB[i] = hasMp[(size_t)b * rowStride + i] ? 0 : 1;
     /* the node of every query, and that node's run in the frame's feature vector (the lockstep walk of :290-420 is a merge join) */
     for (int e = tid; e < nnA; e += SB_NT) {
         const int node = nodesA[e];
@@ -251,18 +253,27 @@ __global__ void __launch_bounds__(SB_NT) k_search_by_bow(int maxF, const int* __
         }
     }
     __syncthreads();
+    /* Rounds.  A frame feature counts as matched for query q iff a query BEFORE q took it (or it was occupied from the start): queries
+     * become final out of order, and an earlier one must not see what a later one took.
+     * A query can only ever take a frame feature at a distance <= TH_LOW (whatever earlier queries do to its candidate set, the feature
+     * it takes is its best one, and that must pass the threshold): only those get its stamp.  With stamps on the node's whole run the
+     * queries of a node would resolve one per round even when nothing matches. */
+#define SB_TAKEN_FOR(row, q) ((unsigned)s.takenBy[row] <= (unsigned)(q))   /* stored q' + 1 <= q  <=>  q' < q; pending and free values are >= 0x8000 */
     for (;;) {
         for (int i = tid; i < maxF; i += SB_NT) {
             s.owner[i] = INT_MAX;
-            if (takenB[i] & 2) takenB[i] = 1;
+            const unsigned v = s.takenBy[i];
+            if ((v & SB_PENDING) && v != SB_FREE) s.takenBy[i] = (uint16_t)(v & ~SB_PENDING);
         }
         __syncthreads();
         for (int q = tid; q < nq; q += SB_NT) {
             if (stateB[q]) continue;
             const uint32_t rg = s.range[q];
+            const int rowA = featsA[q];
+            const uint4 qa = __ldg(descA + 2 * rowA), qb = __ldg(descA + 2 * rowA + 1);
             for (int j = rg & 0xFFFF; j < (int)(rg >> 16); j++) {
                 const int row = featsB[j];
-                if (!(takenB[row] & 1)) atomicMin(&s.owner[row], q);
+                if (!SB_TAKEN_FOR(row, q) && bow_ham(qa, qb, __ldg(descB + 2 * row), __ldg(descB + 2 * row + 1)) <= thLow) atomicMin(&s.owner[row], q);
             }
         }
         __syncthreads();
@@ -276,7 +287,7 @@ __global__ void __launch_bounds__(SB_NT) k_search_by_bow(int maxF, const int* __
             int best1R = 256, best2R = 256, bestIdxR = -1;        /* fisheye rig: the frame's right-camera rows compete separately (:330-358) */
             for (int j = rg & 0xFFFF; j < (int)(rg >> 16); j++) {
                 const int row = featsB[j];
-                if (takenB[row] & 1) continue;                    /* if(vpMapPointMatches[realIdxF]) continue; */
+                if (SB_TAKEN_FOR(row, q)) continue;               /* if(vpMapPointMatches[realIdxF]) continue; */
                 const int dist = bow_ham(qa, qb, __ldg(descB + 2 * row), __ldg(descB + 2 * row + 1));
                 if (nLeftF < 0 || row < nLeftF) {
                     if (dist < best1) { best2 = best1; best1 = dist; bestIdx = row; }
@@ -290,7 +301,7 @@ __global__ void __launch_bounds__(SB_NT) k_search_by_bow(int maxF, const int* __
             bool blocked = false;
             for (int j = rg & 0xFFFF; j < (int)(rg >> 16) && !blocked; j++) {
                 const int row = featsB[j];
-                if ((takenB[row] & 1) || s.owner[row] >= q) continue;
+                if (SB_TAKEN_FOR(row, q) || s.owner[row] >= q) continue;
                 if (bow_ham(qa, qb, __ldg(descB + 2 * row), __ldg(descB + 2 * row + 1)) <= reach) blocked = true;
             }
             if (blocked) { pending++; continue; }
@@ -300,17 +311,12 @@ __global__ void __launch_bounds__(SB_NT) k_search_by_bow(int maxF, const int* __
             const bool okR = !kfkf && nLeftF >= 0 && th1 && bestIdxR >= 0 && best1R <= thLow;
             stateB[q] = 1;
             if (ko) { orbfe_match m; m.best1 = best1; m.best2 = best2; m.idx = bestIdx; m.accepted = ok ? 1 : 0; ko[rowA] = m; }
-            if (ok) {
-                mF[bestIdx] = rowA;
-                atomicOr(&s.taken[bestIdx >> 2], 2u << (8 * (bestIdx & 3)));
-            }
-            if (okR) {
-                mF[bestIdxR] = rowA;
-                atomicOr(&s.taken[bestIdxR >> 2], 2u << (8 * (bestIdxR & 3)));
-            }
+            if (ok) { mF[bestIdx] = rowA; s.takenBy[bestIdx] = (uint16_t)((q + 1) | SB_PENDING); }
+            if (okR) { mF[bestIdxR] = rowA; s.takenBy[bestIdxR] = (uint16_t)((q + 1) | SB_PENDING); }
         }
         if (__syncthreads_count(pending) == 0) break;
     }
+#undef SB_TAKEN_FOR
     /* rotation consistency (:368-384, 440-458) */
     if (checkOri) {
         const float factor = 1.0f / 30.0f;

@@ -333,6 +333,48 @@ def test_gpu_search_by_bow_matches_oracle():
 
 
 @pytest.mark.gpu
+def test_gpu_search_by_bow_under_heavy_competition():
+    """Descriptors from a handful of clusters a few bits apart, two vocabulary nodes: every keyframe feature could take dozens of frame
+    features and most of them compete for the same ones, so the out-of-order resolution of the kernel (a query is final as soon as no
+    earlier unresolved one can take a feature it cares about; a feature counts as matched only for the queries behind its taker) has to
+    reproduce the serial loop exactly — including the best / second-best records of the queries that end up without a match."""
+    from oracle.orb_oracle import KP_DTYPE
+    from orb_slam3_detailed_comments_kor_b200 import bow as B
+    seen = []
+    for seed, n_kf, n_f, clusters, noise, ratio, th in [(1, 600, 700, 3, 8, 0.9, 50), (2, 1500, 1500, 6, 14, 0.7, 50), (3, 900, 400, 2, 5, 0.95, 30), (4, 2000, 2500, 12, 20, 0.8, 50)]:
+        rng = np.random.RandomState(seed)
+        rows = make_vocabulary(seed + 40, 2, 1)
+        voc = O.OracleVocabulary(2, 1, 0, 0, *rows)
+        centres = rng.randint(0, 256, (clusters, 32)).astype(np.uint8)
+
+        def feats(n):
+            d = centres[rng.randint(0, clusters, n)].copy()
+            for i in range(n):
+                for b in rng.randint(0, 256, int(rng.randint(0, noise + 1))):
+                    d[i, b >> 3] ^= np.uint8(1 << (b & 7))
+            k = np.zeros(n, KP_DTYPE)
+            k["x"], k["y"], k["angle"] = rng.uniform(0, 700, n), rng.uniform(0, 400, n), rng.uniform(0, 360, n)
+            return d, k
+        (d_kf, k_kf), (d_f, k_f) = feats(n_kf), feats(n_f)
+        has_mp = (rng.uniform(size=n_kf) < 0.8).astype(np.uint8)
+        fv_kf, fv_f = voc.transform(d_kf, 0)["feat_vec"], voc.transform(d_f, 0)["feat_vec"]
+        for ori in (False, True):
+            want = O.search_by_bow(d_kf, k_kf, fv_kf, has_mp, d_f, k_f, fv_f, th, ratio, ori)
+            got = B.search_by_bow(d_kf, k_kf, fv_kf, has_mp, d_f, k_f, fv_f, th, ratio, ori)
+            assert np.array_equal(got[0], want[0]) and got[2] == want[2] and np.array_equal(got[1], want[1]), (seed, ori)
+            want = O.search_by_bow(d_kf, k_kf, fv_kf, has_mp, d_f, k_f, fv_f, th, ratio, ori, n_left_f=n_f // 2)
+            got = B.search_by_bow(d_kf, k_kf, fv_kf, has_mp, d_f, k_f, fv_f, th, ratio, ori, n_left_f=n_f // 2)
+            assert np.array_equal(got[0], want[0]) and got[2] == want[2] and np.array_equal(got[1], want[1]), (seed, ori, "rig")
+        mp_f = (rng.uniform(size=n_f) < 0.7).astype(np.uint8)
+        want = O.search_by_bow(d_kf, k_kf, fv_kf, has_mp, d_f, k_f, fv_f, th, ratio, True, kf_kf=True, has_map_point_f=mp_f)
+        got = B.search_by_bow(d_kf, k_kf, fv_kf, has_mp, d_f, k_f, fv_f, th, ratio, True, kf_kf=True, has_map_point_f=mp_f)
+        assert np.array_equal(got[0], want[0]) and got[2] == want[2] and np.array_equal(got[1], want[1]), (seed, "kf-kf")
+        seen.append(int(want[2]))
+    print("matches per configuration (kf-kf):", seen)
+    assert sum(seen) > 20
+
+
+@pytest.mark.gpu
 def test_gpu_extract_bow_search_chain_on_device():
     """Tracking's relocalisation path end to end on the device: extract a batch, ComputeBoW, SearchByBoW between frame pairs."""
     import ctypes as C

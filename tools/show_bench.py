@@ -19,3 +19,5 @@ for l in sys.stdin:
     print("projection", d.get("projection"), "| rectify %.0f frames/s" % (d.get("rectify") or {}).get("value", 0))
     print("bow", d.get("bow"))
     print("initialization", d.get("initialization"), "| serial step ms", (d.get("config") or {}).get("serial_ms_per_step"))
+    print("consumers", d.get("consumers"))
+    print("cpu consumers", {k: (d.get("cpu_baseline") or {}).get(k) for k in ("search_by_bow", "search_for_triangulation", "distinctive_descriptors", "initialization")})
