@@ -911,7 +911,7 @@ def main():
     torch.cuda.synchronize()
 
     def pj_step():
-        PJ.search_by_projection_device(PF, 4096, pj_d["kps"].data_ptr(), pj_d["desc"].data_ptr(), pj_d["koff"].data_ptr(), pj_d["grid"].data_ptr(),
+        PJ.search_by_projection_device(PF, 1200, pj_d["kps"].data_ptr(), pj_d["desc"].data_ptr(), pj_d["koff"].data_ptr(), pj_d["grid"].data_ptr(),
                                        pj_d["queries"].data_ptr(), pj_d["qdesc"].data_ptr(), pj_d["qoff"].data_ptr(), pj_out.data_ptr(),
                                        d_u_right=pj_d["u_right"].data_ptr(), d_taken_in=pj_d["taken"].data_ptr(), device=local_rank, stream=st)
 

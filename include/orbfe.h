@@ -451,7 +451,8 @@ typedef struct orbfe_proj_match {
 /* A batch of frames, everything on the device, asynchronous on `stream`, no allocation.
  *   d_kps / d_desc: the frames' keypoints (pt and octave are read: mvKeysUn for a rectified rig, mvKeys followed by mvKeysRight
  *     for a fisheye rig) and 32-byte descriptors, frame f = rows [d_kp_offsets[f], d_kp_offsets[f+1]); at most max_keypoints
- *     (<= 4096) rows per frame, a frame with more gets ORBFE_PS_CAPACITY in every result;
+ *     (<= 4096) rows per frame, a frame with more gets ORBFE_PS_CAPACITY in every result (the CTA's shared memory is sized by
+ *     max_keypoints: pass what the frames really hold, not the limit); at most 65534 queries per frame;
  *   d_n_left: per frame F.Nleft (-1: one grid), or NULL for all -1;   d_u_right: mvuRight per row, or NULL;
  *   d_partner: per row the row matched in the other camera (mvLeftToRightMatch[i] + Nleft / mvRightToLeftMatch[i - Nleft]) or
  *     -1, or NULL;   d_taken_in: per row, nonzero iff F.mvpMapPoints[row] has observations (NULL: none);
@@ -467,6 +468,8 @@ int orbfe_search_by_projection_device(int device, int nframes, int max_keypoints
                                       const uint8_t* d_taken_in, const orbfe_frame_grid* d_grids, const orbfe_proj_query* d_queries,
                                       const uint8_t* d_qdesc, const int32_t* d_q_offsets, int th_high, float nnratio, int check_orientation,
                                       const float* d_inv_level_sigma2, orbfe_proj_match* d_out, uint8_t* d_taken_out, void* stream);
+/* Diagnostics (synchronises the device): maximum and sum over the frames of the speculative rounds the projection kernel needed since the last call. */
+int orbfe_debug_projection_rounds(int* max_rounds, int* sum_rounds);
 /* One frame over host memory (copies inside, synchronous).  taken is updated in place (may be NULL); *nmatches receives the
  * reference's return value (an accepted row with a stereo partner counts twice). */
 int orbfe_search_by_projection(int device, const orbfe_keypoint* kps, const uint8_t* desc, int n, int n_left, const float* u_right,

@@ -32,15 +32,36 @@
 #define PJ_ROWS 48
 #define PJ_CELLS (PJ_COLS * PJ_ROWS)
 #define PJ_PENDING (-1)
+#define PJ_FREE16 0xFFFFu
+#define PJ_MAXQ 65534       /* queries per frame: their indices + 1 live in 16 bits */
+/* occupied as far as query q is concerned: before the search, or by a query in front of q (queries become final out of order) */
+#define PJ_TAKEN_FOR(s, row, q) (((s).taken[row] & 0xFFFFu) <= (unsigned)(q))
 #define PJ_FRONT 2048   /* only the earliest PJ_FRONT unresolved queries take part in a round */
 
+__device__ int g_pjRoundsMax, g_pjRoundsSum;   /* diagnostics: rounds of the last launches (orbfe_debug_projection_rounds) */
+
+/* Shared memory of one CTA, carved from the dynamic block by the launch's max_keypoints (the caller's promise about the frames): a
+ * tracking-sized frame (1200-2000 keypoints) needs 36-44 KB and five CTAs share an SM; the full 4096 need 64 KB. */
 struct PjSmem {
-    int cellEnd[2 * PJ_CELLS];      /* end of each cell's run in `sorted` (start = end of the cell before) */
-    int owner[PJ_MAXKP];
-    uint16_t sorted[PJ_MAXKP];
-    uint32_t taken[PJ_MAXKP / 4];   /* one byte per keypoint: bit 0 taken, bit 1 taken as of the next round */
-    int warpSum[PJ_NT / 32];
+    int* cellEnd;        /* [PJ_CELLS, twice with rigs in the batch] end of each cell's run in `sorted` (start = end of the cell before) */
+    int* owner;          /* [maxKp] */
+    uint32_t* taken;     /* [maxKp] low half: 1 + the first query that took the keypoint (0: occupied before the search), PJ_FREE16 = nobody;
+                            high half: the same for the takes of the running round, which become visible with the next one */
+    uint16_t* sorted;    /* [maxKp] */
+    int* warpSum;        /* [PJ_NT / 32] */
 };
+static __host__ __device__ inline size_t pj_smem_bytes(int maxKp, bool rigs) { return (size_t)(rigs ? 2 : 1) * PJ_CELLS * 4 + (size_t)((maxKp + 3) & ~3) * 10 + (PJ_NT / 32) * 4; }
+/* a stereo partner row is overwritten unconditionally (src/ORBmatcher.cc:130-133), so a row can be taken more than once: what counts for a
+ * query is whether ANY query before it did, i.e. the smallest taker */
+static __device__ __forceinline__ void pj_take(const PjSmem& s, int row, int q) {
+    uint32_t old = s.taken[row];
+    for (;;) {
+        const uint32_t hi = min(old >> 16, (uint32_t)(q + 1));
+        const uint32_t seen = atomicCAS(&s.taken[row], old, (hi << 16) | (old & 0xFFFFu));
+        if (seen == old) break;
+        old = seen;
+    }
+}
 
 struct PjFrame {
     const orbfe_keypoint* kps;
@@ -91,6 +112,7 @@ static __device__ __forceinline__ void pj_window(const PjFrame& fr, const PjSmem
     if (y0 >= PJ_ROWS) return;
     const int y1 = min(PJ_ROWS - 1, (int)ceilf((ay + r) * fr.invh));
     if (y1 < 0) return;
+    if ((p.flags & ORBFE_PQ_RIGHT) && fr.nLeft < 0) return;   /* no right camera: mGridRight is empty (and not even allocated here) */
     const int side = (p.flags & ORBFE_PQ_RIGHT) ? PJ_CELLS : 0;
     for (int ix = x0; ix <= x1; ix++) {
         const int c0 = side + ix * PJ_ROWS + y0, c1 = side + ix * PJ_ROWS + y1;
@@ -114,7 +136,16 @@ __global__ void __launch_bounds__(PJ_NT) k_search_by_projection(int maxKp, const
                                                                 const int32_t* __restrict__ qOff, int thHigh, float nnratio, int checkOri,
                                                                 const float* __restrict__ invSigma2, orbfe_proj_match* out, uint8_t* __restrict__ takenOut) {
     extern __shared__ __align__(16) unsigned char pj_raw[];
-    PjSmem& s = *reinterpret_cast<PjSmem*>(pj_raw);
+    const int nCells = nLeftAll ? 2 * PJ_CELLS : PJ_CELLS;   /* the second grid (mGridRight) only exists with fisheye rigs in the batch */
+    PjSmem s;
+    {
+        const int cap = (maxKp + 3) & ~3;
+        s.cellEnd = reinterpret_cast<int*>(pj_raw);
+        s.owner = s.cellEnd + nCells;
+        s.taken = reinterpret_cast<uint32_t*>(s.owner + cap);
+        s.sorted = reinterpret_cast<uint16_t*>(s.taken + cap);
+        s.warpSum = reinterpret_cast<int*>(s.sorted + cap);
+    }
     const int tid = threadIdx.x, f = blockIdx.x;
     const int k0 = kpOff[f], q0 = qOff[f], nq = qOff[f + 1] - q0;
     PjFrame fr;
@@ -133,7 +164,7 @@ __global__ void __launch_bounds__(PJ_NT) k_search_by_projection(int maxKp, const
     volatile int* status = &res[0].status; /* stride 7 ints; PJ_PENDING while unresolved */
     __shared__ int s_rot[32];
 
-    if (fr.n > maxKp || fr.n > PJ_MAXKP || fr.n < 0) { /* the caller's promise about the frame size does not hold */
+    if (fr.n > maxKp || fr.n > PJ_MAXKP || fr.n < 0 || nq > PJ_MAXQ) { /* the caller's promise about the frame size does not hold */
         for (int q = tid; q < nq; q += PJ_NT) {
             orbfe_proj_match m;
             m.best_idx = -1; m.best_dist = 256; m.best_level = -1; m.second_dist = 256; m.second_level = -1; m.accepted = 0; m.status = ORBFE_PS_CAPACITY;
@@ -145,10 +176,9 @@ __global__ void __launch_bounds__(PJ_NT) k_search_by_projection(int maxKp, const
     const bool stereoRig = fr.nLeft >= 0 && fr.partner != nullptr;
 
     /* ---- grid: AssignFeaturesToGrid as a counting sort ---- */
-    for (int i = tid; i < 2 * PJ_CELLS; i += PJ_NT) s.cellEnd[i] = 0;
-    for (int i = tid; i < PJ_MAXKP / 4; i += PJ_NT) s.taken[i] = 0;
+    for (int i = tid; i < nCells; i += PJ_NT) s.cellEnd[i] = 0;
+    for (int i = tid; i < fr.n; i += PJ_NT) s.taken[i] = 0xFFFFFFFFu;
     __syncthreads();
-    uint8_t* takenB = reinterpret_cast<uint8_t*>(s.taken);
     for (int i = tid; i < fr.n; i += PJ_NT) {
         const float x = __ldg(&fr.kps[i].x), y = __ldg(&fr.kps[i].y);
         const int px = (int)roundf((x - fr.minx) * fr.invw), py = (int)roundf((y - fr.miny) * fr.invh);
@@ -158,11 +188,11 @@ __global__ void __launch_bounds__(PJ_NT) k_search_by_projection(int maxKp, const
             atomicAdd(&s.cellEnd[c], 1);
         }
         s.owner[i] = c;
-        takenB[i] = (takenIn && takenIn[k0 + i]) ? 1 : 0;
+        if (takenIn && takenIn[k0 + i]) s.taken[i] = 0xFFFF0000u;
     }
     __syncthreads();
     {   /* exclusive scan of the 6144 counts: 24 consecutive cells per thread */
-        const int per = 2 * PJ_CELLS / PJ_NT, base = tid * per;
+        const int per = nCells / PJ_NT, base = tid * per;
         int sum = 0;
         for (int i = 0; i < per; i++) sum += s.cellEnd[base + i];
         int incl = sum;
@@ -187,7 +217,7 @@ __global__ void __launch_bounds__(PJ_NT) k_search_by_projection(int maxKp, const
         if (c >= 0) s.sorted[atomicAdd(&s.cellEnd[c], 1)] = (uint16_t)i;   /* cellEnd[c] ends up as the end of cell c */
     }
     __syncthreads();
-    for (int c = tid; c < 2 * PJ_CELLS; c += PJ_NT) {   /* ascending rows inside each cell (the lists are a few entries long) */
+    for (int c = tid; c < nCells; c += PJ_NT) {   /* ascending rows inside each cell (the lists are a few entries long) */
         const int beg = c ? s.cellEnd[c - 1] : 0, end = s.cellEnd[c];
         for (int i = beg + 1; i < end; i++) {
             const uint16_t v = s.sorted[i];
@@ -210,10 +240,12 @@ __global__ void __launch_bounds__(PJ_NT) k_search_by_projection(int maxKp, const
      * of all EARLIER unresolved queries, and those are inside the front by construction. */
     __shared__ int s_front;
     int myFirst = tid;   /* my first query that may still be unresolved (I own tid, tid + PJ_NT, ...) */
+    int rounds = 0;
     for (;;) {
         for (int i = tid; i < fr.n; i += PJ_NT) {
             s.owner[i] = INT_MAX;
-            if (takenB[i] & 2) takenB[i] = 1;
+            const uint32_t w = s.taken[i];
+            if ((w >> 16) != PJ_FREE16) s.taken[i] = 0xFFFF0000u | min(w & 0xFFFFu, w >> 16);
         }
         if (tid == 0) s_front = INT_MAX;
         __syncthreads();
@@ -227,9 +259,14 @@ __global__ void __launch_bounds__(PJ_NT) k_search_by_projection(int maxKp, const
             const orbfe_proj_query p = qs[q];
             if (p.flags & (ORBFE_PQ_AFTER_LEFT | ORBFE_PQ_NEEDS_LEFT_WINDOW))
                 res[q].accepted = (q > 0 && status[(q - 1) * 7] == PJ_PENDING) ? 0 : 1;   /* may I look at q-1 in step B? */
+            if (!(p.flags & ORBFE_PQ_BLOCKS)) continue;   /* a map point without observations occupies nothing: no stamps */
+            /* what a query takes is its best candidate, and that has to be within thHigh: only those rows (and their partners) get its
+             * stamp.  With stamps on the whole window, queries whose windows overlap resolved one per round whether or not they competed. */
+            const uint4 sa = __ldg(qdesc + 2 * q), sb = __ldg(qdesc + 2 * q + 1);
             pj_window(fr, s, p, [&](int row, int oct) {
-                if (takenB[row] & 1) return;
+                if (PJ_TAKEN_FOR(s, row, q)) return;
                 if (pj_gated(fr, p, row, oct, gateRight)) return;
+                if (pj_ham(sa, sb, __ldg(fr.desc + 2 * row), __ldg(fr.desc + 2 * row + 1)) > thHigh) return;
                 atomicMin(&s.owner[row], q);
                 if (stereoRig) {
                     const int pt = __ldg(fr.partner + row);
@@ -258,7 +295,7 @@ __global__ void __launch_bounds__(PJ_NT) k_search_by_projection(int maxKp, const
             int bestDist = 256, bestLevel = -1, bestDist2 = 256, bestLevel2 = -1, bestIdx = -1, seen = 0;
             pj_window(fr, s, p, [&](int row, int oct) {
                 seen++;
-                if (takenB[row] & 1) return;
+                if (PJ_TAKEN_FOR(s, row, q)) return;
                 if (pj_gated(fr, p, row, oct, gateRight)) return;
                 const int dist = pj_ham(qa, qb, __ldg(fr.desc + 2 * row), __ldg(fr.desc + 2 * row + 1));
                 if (dist < bestDist) { bestDist2 = bestDist; bestDist = dist; bestLevel2 = bestLevel; bestLevel = oct; bestIdx = row; }
@@ -273,7 +310,7 @@ __global__ void __launch_bounds__(PJ_NT) k_search_by_projection(int maxKp, const
                      : (!bestOnly && bestLevel == bestLevel2 && (float)bestDist > nnratio * (float)bestDist2) ? ORBFE_PS_RATIO_REJECTED : ORBFE_PS_ACCEPTED;
                 const int reach = bestDist2;   /* candidates above it cannot change any reported field */
                 pj_window(fr, s, p, [&](int row, int oct) {
-                    if (blocked || (takenB[row] & 1)) return;
+                    if (blocked || PJ_TAKEN_FOR(s, row, q)) return;
                     if (pj_gated(fr, p, row, oct, gateRight)) return;
                     if (s.owner[row] < q && pj_ham(qa, qb, __ldg(fr.desc + 2 * row), __ldg(fr.desc + 2 * row + 1)) <= reach) blocked = true;
                 });
@@ -288,12 +325,14 @@ __global__ void __launch_bounds__(PJ_NT) k_search_by_projection(int maxKp, const
             m.accepted = st == ORBFE_PS_ACCEPTED ? 1 : 0; m.status = st;
             res[q] = m;
             if (st == ORBFE_PS_ACCEPTED && (p.flags & ORBFE_PQ_BLOCKS)) {
-                atomicOr(&s.taken[bestIdx >> 2], 2u << (8 * (bestIdx & 3)));
-                if (partnerRow >= 0) atomicOr(&s.taken[partnerRow >> 2], 2u << (8 * (partnerRow & 3)));
+                pj_take(s, bestIdx, q);
+                if (partnerRow >= 0) pj_take(s, partnerRow, q);
             }
         }
+        rounds++;
         if (__syncthreads_count(pending) == 0) break;
     }
+    if (tid == 0) { atomicMax(&g_pjRoundsMax, rounds); atomicAdd(&g_pjRoundsSum, rounds); }
     /* ---- rotation consistency (ORBmatcher.cc:2305-2322, 2391-2412): histogram of kpLF.angle - kpCF.angle over the matches ---- */
     if (checkOri) {
         const float factor = 1.0f / 30.0f;   /* 1.0f/HISTO_LENGTH */
@@ -332,16 +371,29 @@ __global__ void __launch_bounds__(PJ_NT) k_search_by_projection(int maxKp, const
             if (bin >= 0 && bin < 30 && bin != ind1 && bin != ind2 && bin != ind3) {
                 res[q].accepted = 0;
                 status[q * 7] = ORBFE_PS_ROTATION;
-                takenB[row] = 0;                 /* mvpMapPoints[row] = NULL */
+                s.taken[row] = 0xFFFFFFFFu;      /* mvpMapPoints[row] = NULL */
             }
         }
         __syncthreads();
     }
     if (takenOut)
-        for (int i = tid; i < fr.n; i += PJ_NT) takenOut[k0 + i] = takenB[i] ? 1 : 0;
+        for (int i = tid; i < fr.n; i += PJ_NT) takenOut[k0 + i] = s.taken[i] != 0xFFFFFFFFu ? 1 : 0;
 }
 
 extern "C" {
+
+/* diagnostics: maximum and sum over the CTAs (frames) of the rounds k_search_by_projection needed since the last call; resets both */
+int orbfe_debug_projection_rounds(int* max_rounds, int* sum_rounds) {
+    int z = 0, a = 0, b = 0;
+    ORBFE_CUDA(cudaDeviceSynchronize());
+    ORBFE_CUDA(cudaMemcpyFromSymbol(&a, g_pjRoundsMax, sizeof a));
+    ORBFE_CUDA(cudaMemcpyFromSymbol(&b, g_pjRoundsSum, sizeof b));
+    ORBFE_CUDA(cudaMemcpyToSymbol(g_pjRoundsMax, &z, sizeof z));
+    ORBFE_CUDA(cudaMemcpyToSymbol(g_pjRoundsSum, &z, sizeof z));
+    if (max_rounds) *max_rounds = a;
+    if (sum_rounds) *sum_rounds = b;
+    return ORBFE_OK;
+}
 
 int orbfe_search_by_projection_device(int device, int nframes, int max_keypoints, const orbfe_keypoint* d_kps, const uint8_t* d_desc,
                                       const int32_t* d_kp_offsets, const int32_t* d_n_left, const float* d_u_right, const int32_t* d_partner,
@@ -354,10 +406,10 @@ int orbfe_search_by_projection_device(int device, int nframes, int max_keypoints
     ORBFE_CUDA(cudaSetDevice(device));
     static thread_local int configured = -1;
     if (configured != device) {
-        ORBFE_CUDA(cudaFuncSetAttribute(k_search_by_projection, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(PjSmem)));
+        ORBFE_CUDA(cudaFuncSetAttribute(k_search_by_projection, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pj_smem_bytes(PJ_MAXKP, true)));
         configured = device;
     }
-    k_search_by_projection<<<nframes, PJ_NT, sizeof(PjSmem), (cudaStream_t)stream>>>(max_keypoints, d_kps, d_desc, d_kp_offsets, d_n_left, d_u_right, d_partner,
+    k_search_by_projection<<<nframes, PJ_NT, pj_smem_bytes(max_keypoints, d_n_left != nullptr), (cudaStream_t)stream>>>(max_keypoints, d_kps, d_desc, d_kp_offsets, d_n_left, d_u_right, d_partner,
                                                                                     d_taken_in, d_grids, d_queries, d_qdesc, d_q_offsets, th_high, nnratio,
                                                                                     check_orientation ? 1 : 0, d_inv_level_sigma2, d_out, d_taken_out);
     ORBFE_CUDA(cudaGetLastError());
