@@ -929,6 +929,33 @@ def main():
                   "ms_per_step": pj_ms, "frames_per_step": PF * world, "keypoints_per_frame": 1200, "map_points_per_frame": int(pj_qoff[1]),
                   "accepted_per_step": pj_acc, "note": "ORBmatcher::SearchByProjection(Frame&, vpMapPoints, th=1) incl. the frame grid; device resident"}
 
+    # the tracker's per-frame call: SearchByProjection(CurrentFrame, LastFrame, th = 7, bMono = false) with the rotation check
+    lf_cases = [PC.make_case(seed=950 + i, n=1200, nq=1200, W=W, H=H, th=7.0, stereo_gate=True, last_frame="still") for i in range(8)]
+    lf_order = [lf_cases[i % 8] for i in range(PF)]
+    lf_cat = lambda k: np.concatenate([c[k] for c in lf_order])  # noqa: E731
+    lf_koff = np.cumsum([0] + [len(c["kps"]) for c in lf_order]).astype(np.int32)
+    lf_qoff = np.cumsum([0] + [len(c["queries"]) for c in lf_order]).astype(np.int32)
+    lf_d = {k: to_dev(lf_cat(k)) for k in ("kps", "desc", "queries", "qdesc", "u_right", "taken")}
+    lf_d["grid"], lf_d["koff"], lf_d["qoff"] = to_dev(np.stack([c["grid"] for c in lf_order])), to_dev(lf_koff), to_dev(lf_qoff)
+    lf_out = torch.zeros(int(lf_qoff[-1]) * 28, dtype=torch.uint8, device="cuda")
+
+    def lf_step():
+        PJ.search_by_projection_device(PF, 1200, lf_d["kps"].data_ptr(), lf_d["desc"].data_ptr(), lf_d["koff"].data_ptr(), lf_d["grid"].data_ptr(),
+                                       lf_d["queries"].data_ptr(), lf_d["qdesc"].data_ptr(), lf_d["qoff"].data_ptr(), lf_out.data_ptr(),
+                                       d_u_right=lf_d["u_right"].data_ptr(), d_taken_in=lf_d["taken"].data_ptr(), check_orientation=True, device=local_rank, stream=st)
+    for _ in range(3):
+        lf_step()
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        lf_step()
+    e1.record()
+    barrier()
+    lf_ms = max_over_ranks(e0.elapsed_time(e1) / args.steps)
+    projection["last_frame"] = {"frames_per_s": PF * world / (lf_ms / 1e3), "ms_per_step": lf_ms, "frames_per_step": PF * world, "map_points_per_frame": 1200,
+                                "accepted_per_step": int(lf_out.cpu().numpy().view(PJ.PROJ_MATCH_DTYPE)["accepted"].sum()),
+                                "note": "ORBmatcher::SearchByProjection(CurrentFrame, LastFrame, th=7, bMono=false) with the rotation check (TrackWithMotionModel)"}
+
     # ---- ORBmatcher::SearchForInitialization: pairs of frames from the initial extractor (5 x nFeatures keypoints, of
     #      which about 22 % are on level 0 and take part), window 100 px, one CTA per pair
     def init_case(seed, n=5 * PARAMS[0], clusters=150, noise=20):
@@ -1116,6 +1143,13 @@ def main():
         idt = time.perf_counter() - t0
         cpu["initialization"] = {"value": 4 * cores / idt, "unit": "frame_pairs/s", "kind": "reference" if reference_available() else "port",
                                  "sample": "%d pairs (%.2f s wall) pair-parallel over %d threads" % (4 * cores, idt, cores)}
+        t0 = time.perf_counter()
+        with ThreadPoolExecutor(cores) as tp:
+            list(tp.map(lambda i: O.search_by_projection(lf_cases[i % 8]["kps"], lf_cases[i % 8]["desc"], lf_cases[i % 8]["queries"], lf_cases[i % 8]["qdesc"],
+                                                         lf_cases[i % 8]["grid"], u_right=lf_cases[i % 8]["u_right"], taken=lf_cases[i % 8]["taken"], check_orientation=True),
+                        range(16 * cores)))
+        ldt = time.perf_counter() - t0
+        cpu["projection_last_frame"] = {"value": 16 * cores / ldt, "unit": "frames/s", "kind": "port", "sample": "%d frames (%.2f s wall) frame-parallel over %d threads" % (16 * cores, ldt, cores)}
         cpu["projection"] = {"value": reps * int(pj_qoff[1]) / pdt, "unit": "map_point_searches/s",
                              "sample": "%d frames (%.2f s wall) frame-parallel over %d threads" % (reps, pdt, cores)}
 
