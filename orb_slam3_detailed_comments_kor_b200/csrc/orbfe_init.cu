@@ -25,6 +25,7 @@
 #define SI_COLS 64
 #define SI_ROWS 48
 #define SI_CELLS (SI_COLS * SI_ROWS)
+#define SI_CACHE 1536
 
 struct SiSmem {
     int cellEnd[SI_CELLS];       /* end of each cell's run in `sorted` */
@@ -35,6 +36,11 @@ struct SiSmem {
     uint16_t qList[SI_MAXKP];    /* the level-0 rows of F1, ascending */
     int warpSum[SI_NT / 32];
     int rot[32];
+    /* the level-0 keypoints of F2 in `sorted` order, when there are at most SI_CACHE of them (the usual case: a fifth of the keypoints are
+     * on level 0): every round reads every candidate's position and descriptor, 150 candidates per query, and from global memory that
+     * is L2 bandwidth (8 MB per round and pair) */
+    uint4 cDesc[SI_CACHE][2];
+    float2 cXy[SI_CACHE];
 };
 
 static __device__ __forceinline__ int si_ham(const uint4 qa, const uint4 qb, const uint4 a, const uint4 b) {
@@ -127,6 +133,14 @@ __global__ void __launch_bounds__(SI_NT) k_search_for_initialization(const orbfe
                  return (px >= 0 && px < SI_COLS && py >= 0 && py < SI_ROWS) ? px * SI_ROWS + py : -1;
              },
              [](int i) { return i; });
+    const int n2lvl0 = s.cellEnd[SI_CELLS - 1];
+    const bool cached = n2lvl0 <= SI_CACHE;
+    if (cached)
+        for (int j = tid; j < n2lvl0; j += SI_NT) {
+            const int i2 = s.sorted[j];
+            s.cDesc[j][0] = __ldg(desc2 + 2 * i2); s.cDesc[j][1] = __ldg(desc2 + 2 * i2 + 1);
+            s.cXy[j] = make_float2(__ldg(&kps2[i2].x), __ldg(&kps2[i2].y));
+        }
     /* ---- the level-0 keypoints of F1, in order ---- */
     if (tid == 0) { s_nq = 0; s_minChanged = -1; }
     for (int i = tid; i < n1; i += SI_NT) { s.state[0][i] = 0; s.state[1][i] = 0; matches[i] = -1; }
@@ -176,8 +190,9 @@ __global__ void __launch_bounds__(SI_NT) k_search_for_initialization(const orbfe
                     const int beg = c0 ? s.cellEnd[c0 - 1] : 0, end = s.cellEnd[c1];
                     for (int j = beg; j < end; j++) {
                         const int i2 = s.sorted[j];
-                        if (!(fabsf(__ldg(&kps2[i2].x) - x) < r && fabsf(__ldg(&kps2[i2].y) - y) < r)) continue;
-                        const int dist = si_ham(qa, qb, __ldg(desc2 + 2 * i2), __ldg(desc2 + 2 * i2 + 1));
+                        const float2 xy = cached ? s.cXy[j] : make_float2(__ldg(&kps2[i2].x), __ldg(&kps2[i2].y));
+                        if (!(fabsf(xy.x - x) < r && fabsf(xy.y - y) < r)) continue;
+                        const int dist = cached ? si_ham(qa, qb, s.cDesc[j][0], s.cDesc[j][1]) : si_ham(qa, qb, __ldg(desc2 + 2 * i2), __ldg(desc2 + 2 * i2 + 1));
                         int held = INT_MAX;   /* vMatchedDistance[i2] when q's turn comes */
                         for (int w = i2 ? s.wEnd[i2 - 1] : 0, we = s.wEnd[i2]; w < we; w++) {
                             const int qw = s.wq[w];
