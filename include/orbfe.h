@@ -57,6 +57,10 @@ typedef struct orbfe_extractor orbfe_extractor;
 typedef struct orbfe_matcher orbfe_matcher;
 
 const char* orbfe_last_error(void);
+/* The one-frame host entry points of the matchers (orbfe_search_by_projection, orbfe_search_by_bow, orbfe_search_for_triangulation,
+ * orbfe_search_for_initialization) stage their arguments through a block of pinned host and device memory that belongs to the calling
+ * thread; it grows to the largest call seen and is freed when the thread ends, or here. */
+void orbfe_thread_release(void);
 int orbfe_device_count(void);
 const char* orbfe_version(void);
 
@@ -373,7 +377,8 @@ typedef struct {
  * Pinhole::epipolarConstrain (src/CameraModels/Pinhole.cpp:135-157) for d_f12 (F12 of pair p, 9 floats row-major; d_level_sigma2 =
  * pKF2->mvLevelSigma2, 16 floats) or coarse; rotation histogram with check_orientation.  d_u_right (mvuRight, may be NULL) decides
  * bStereo1/2; d_has_map_point as in orbfe_search_by_bow_device (here a row WITH a map point is left out).
- * d_match_12[p*row_stride + i] = vMatches12[i]; d_nmatches[p] = the return value. */
+ * d_match_12[p*row_stride + i] = vMatches12[i]; d_nmatches[p] = the return value.  At most 65535 pairs per call; a pair's vocabulary
+ * nodes are dealt out over up to 16 CTAs, so that the few pairs of one CreateNewMapPoints call still spread over the SMs. */
 int orbfe_search_for_triangulation_device(int device, int npairs, int max_features, const int32_t* d_pair_1, const int32_t* d_pair_2, const uint8_t* d_desc,
                                           const orbfe_keypoint* d_kps, const float* d_u_right, int row_stride, const int32_t* d_fv_nodes,
                                           const int32_t* d_fv_starts, const int32_t* d_fv_feats, const int32_t* d_fv_count, const uint8_t* d_has_map_point,

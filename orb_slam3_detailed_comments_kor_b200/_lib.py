@@ -31,6 +31,7 @@ _lib = None
 vp, i32, i64, f32, f64, sz = C.c_void_p, C.c_int, C.c_int64, C.c_float, C.c_double, C.c_size_t
 SIGNATURES = {
     "orbfe_last_error": (C.c_char_p, []),
+    "orbfe_thread_release": (None, []),
     "orbfe_device_count": (i32, []),
     "orbfe_version": (C.c_char_p, []),
     "orbfe_extractor_create": (i32, [C.POINTER(OrbfeParams), i32, i32, i32, i32, C.POINTER(vp)]),

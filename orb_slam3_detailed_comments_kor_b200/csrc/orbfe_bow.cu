@@ -394,11 +394,9 @@ __global__ void __launch_bounds__(SB_NT) k_search_for_triangulation(int maxF, co
                                                                     const int* __restrict__ fvCount, const uint8_t* __restrict__ hasMp,
                                                                     const float* __restrict__ f12All, const float* __restrict__ epAll,
                                                                     const float* __restrict__ scaleFactors, const float* __restrict__ levelSigma2, int thLow,
-                                                                    int onlyStereo, int coarse, int checkOri, int* __restrict__ match12,
-                                                                    int* __restrict__ nmatches, const TriRig* __restrict__ rigs) {
-    __shared__ int s_rot[32];
-    __shared__ int s_total;
-    const int tid = threadIdx.x, pr = blockIdx.x;
+                                                                    int onlyStereo, int coarse, int* __restrict__ match12,
+                                                                    const TriRig* __restrict__ rigs) {
+    const int tid = threadIdx.x, pr = blockIdx.y;
     const int a = pair1[pr], b = pair2[pr];
     const int* nodesA = fvNodes + (size_t)a * maxF; const int* startsA = fvStarts + (size_t)a * (maxF + 1); const int* featsA = fvFeats + (size_t)a * maxF;
     const int* nodesB = fvNodes + (size_t)b * maxF; const int* startsB = fvStarts + (size_t)b * (maxF + 1); const int* featsB = fvFeats + (size_t)b * maxF;
@@ -409,13 +407,10 @@ __global__ void __launch_bounds__(SB_NT) k_search_for_triangulation(int maxF, co
     const uint8_t* mpA = hasMp ? hasMp + (size_t)a * rowStride : nullptr; const uint8_t* mpB = hasMp ? hasMp + (size_t)b * rowStride : nullptr;
     const float* F = f12All + (size_t)pr * 9;
     const float epx = epAll[2 * pr], epy = epAll[2 * pr + 1];
-    int* m12 = match12 + (size_t)pr * rowStride;
-    for (int i = tid; i < rowStride; i += SB_NT) m12[i] = -1;
-    if (tid < 32) s_rot[tid] = 0;
-    if (tid == 0) s_total = 0;
-    __syncthreads();
-    /* one warp walks the nodes of keyframe 1 in turn (binary search for the node in keyframe 2), its lanes take the node's features */
-    for (int e = tid >> 5; e < nnA; e += SB_NT / 32) {
+    int* m12 = match12 + (size_t)pr * rowStride;                                /* set to -1 by the caller's memset */
+    /* one warp walks nodes of keyframe 1 (binary search for the node in keyframe 2), its lanes take the node's features; the nodes of a pair
+     * are dealt out over the gridDim.x CTAs of its row, so that a single pair still fills the machine */
+    for (int e = blockIdx.x * (SB_NT / 32) + (tid >> 5); e < nnA; e += gridDim.x * (SB_NT / 32)) {
         const int node = nodesA[e];
         int lo = 0, hi = nnB;
         while (lo < hi) { const int mid = (lo + hi) >> 1; if (nodesB[mid] < node) lo = mid + 1; else hi = mid; }
@@ -434,6 +429,42 @@ __global__ void __launch_bounds__(SB_NT) k_search_for_triangulation(int maxF, co
             const float den = __fadd_rn(__fmul_rn(la, la), __fmul_rn(lb, lb));
             const uint4 qa = __ldg(descA + 2 * idx1), qb = __ldg(descA + 2 * idx1 + 1);
             int bestDist = thLow, bestIdx2 = -1;
+            if (RIG && !coarse) {
+                /* The constraint is a pure function of the pair, so the loop of :1060-1140 returns the candidate of smallest distance <= TH_LOW
+                 * (the last one among equals) that passes it.  Candidates are therefore tried in that order, (distance, later first), and the
+                 * first that triangulates wins: never more triangulations than the reference's order makes, and the lanes of the warp
+                 * triangulate together instead of one after another. */
+                const TriRig& rg = rigs[pr];
+                const int r1 = idx1 >= rg.nLeft1 ? 1 : 0;
+                const float s1 = __ldg(levelSigma2 + __ldg(&kA[idx1].octave));
+                unsigned prevKey = 0;
+                for (;;) {
+                    unsigned best = 0xFFFFFFFFu;
+                    for (int c = fb0; c < fb1; c++) {
+                        const int idx2 = featsB[c];
+                        if (mpB && mpB[idx2]) continue;
+                        const int dist = bow_ham(qa, qb, __ldg(descB + 2 * idx2), __ldg(descB + 2 * idx2 + 1));
+                        if (dist > thLow) continue;
+                        const unsigned key = ((unsigned)dist << 16) | (unsigned)(0xFFFF - (c - fb0));
+                        if (key > prevKey && key < best) best = key;
+                    }
+                    if (best == 0xFFFFFFFFu) break;
+                    const int idx2 = featsB[fb0 + (0xFFFF - (int)(best & 0xFFFFu))];
+                    const int r2 = idx2 >= rg.nLeft2 ? 1 : 0, combo = 2 * r1 + r2;   /* ll, lr, rl, rr */
+                    FisheyeRig fr;
+                    fr.c1 = rg.cam[r1]; fr.c2 = rg.cam[2 + r2];
+#pragma unroll
+                    for (int k = 0; k < 9; k++) fr.R12[k] = rg.R[combo][k];
+#pragma unroll
+                    for (int k = 0; k < 3; k++) fr.t12[k] = rg.t[combo][k];
+                    float x3D[3];
+                    if (kb8_triangulate_pair(fr, x1, y1, __ldg(&kB[idx2].x), __ldg(&kB[idx2].y), s1, __ldg(levelSigma2 + __ldg(&kB[idx2].octave)), x3D) > 0.0001f) {
+                        bestIdx2 = idx2;
+                        break;
+                    }
+                    prevKey = best;
+                }
+            } else
             for (int c = fb0; c < fb1; c++) {
                 const int idx2 = featsB[c];
                 if (mpB && mpB[idx2]) continue;                               /* if(vbMatched2[idx2] || pMP2) continue; (vbMatched2 is never set) */
@@ -448,41 +479,41 @@ __global__ void __launch_bounds__(SB_NT) k_search_for_triangulation(int maxF, co
                     if (__fadd_rn(__fmul_rn(dex, dex), __fmul_rn(dey, dey)) < __fmul_rn(100.0f, __ldg(scaleFactors + oct2))) continue;
                 }
                 bool ok = coarse != 0;
-                if (RIG) {
-                    if (!ok) {
-                        const TriRig& rg = rigs[pr];
-                        const int r1 = idx1 >= rg.nLeft1 ? 1 : 0, r2 = idx2 >= rg.nLeft2 ? 1 : 0, combo = 2 * r1 + r2;   /* ll, lr, rl, rr */
-                        FisheyeRig fr;
-                        fr.c1 = rg.cam[r1]; fr.c2 = rg.cam[2 + r2];
-#pragma unroll
-                        for (int k = 0; k < 9; k++) fr.R12[k] = rg.R[combo][k];
-#pragma unroll
-                        for (int k = 0; k < 3; k++) fr.t12[k] = rg.t[combo][k];
-                        float x3D[3];
-                        const int oct1 = __ldg(&kA[idx1].octave);
-                        ok = kb8_triangulate_pair(fr, x1, y1, x2, y2, __ldg(levelSigma2 + oct1), __ldg(levelSigma2 + oct2), x3D) > 0.0001f;
-                    }
-                } else if (!ok && den != 0.0f) {
+                if (!RIG && !ok && den != 0.0f) {
                     const float num = __fadd_rn(__fadd_rn(__fmul_rn(la, x2), __fmul_rn(lb, y2)), lc);
                     const float dsqr = __fdiv_rn(__fmul_rn(num, num), den);
                     ok = (double)dsqr < 3.84 * (double)__ldg(levelSigma2 + oct2);
                 }
                 if (ok) { bestIdx2 = idx2; bestDist = dist; }
             }
-            if (bestIdx2 >= 0) {
-                m12[idx1] = bestIdx2;
-                if (checkOri) {
-                    float rot = __ldg(&kA[idx1].angle) - __ldg(&kB[bestIdx2].angle);
-                    if (rot < 0.0f) rot += 360.0f;
-                    int bin = (int)roundf(rot * (1.0f / 30.0f));
-                    if (bin == 30) bin = 0;
-                    if (bin >= 0 && bin < 30) atomicAdd(&s_rot[bin], 1);
-                }
-            }
+            if (bestIdx2 >= 0) m12[idx1] = bestIdx2;
         }
     }
+}
+
+/* The rotation histogram over a pair's matches (ORBmatcher.cc:1146-1185: only the three fullest 30-degree bins stay) and the count. */
+__global__ void __launch_bounds__(SB_NT) k_triangulation_rotation(const int* __restrict__ pair1, const int* __restrict__ pair2,
+                                                                  const orbfe_keypoint* __restrict__ kps, int rowStride, int checkOri,
+                                                                  int* __restrict__ match12, int* __restrict__ nmatches) {
+    __shared__ int s_rot[32];
+    __shared__ int s_total;
+    const int tid = threadIdx.x, pr = blockIdx.x;
+    const orbfe_keypoint* kA = kps + (size_t)pair1[pr] * rowStride; const orbfe_keypoint* kB = kps + (size_t)pair2[pr] * rowStride;
+    int* m12 = match12 + (size_t)pr * rowStride;
+    if (tid < 32) s_rot[tid] = 0;
+    if (tid == 0) s_total = 0;
     __syncthreads();
     if (checkOri) {
+        for (int i = tid; i < rowStride; i += SB_NT) {
+            const int r2 = m12[i];
+            if (r2 < 0) continue;
+            float rot = __ldg(&kA[i].angle) - __ldg(&kB[r2].angle);
+            if (rot < 0.0f) rot += 360.0f;
+            int bin = (int)roundf(rot * (1.0f / 30.0f));
+            if (bin == 30) bin = 0;
+            if (bin >= 0 && bin < 30) atomicAdd(&s_rot[bin], 1);
+        }
+        __syncthreads();
         if (tid == 0) {
             int ind1 = -1, ind2 = -1, ind3 = -1, max1 = 0, max2 = 0, max3 = 0;
             for (int i = 0; i < 30; i++) {
@@ -706,56 +737,51 @@ int orbfe_search_by_bow(int device, const uint8_t* desc_kf, const orbfe_keypoint
         orbfe_set_error("no usable CUDA device %d (found %d); this library has no CPU path", device, ndev);
         return ORBFE_E_CUDA;
     }
-    ORBFE_CUDA(cudaSetDevice(device));
-    /* two frames (0 = keyframe, 1 = frame) in the strided layout of the batch entry point */
-    std::vector<uint8_t> hDesc((size_t)2 * S * 32, 0), hMp((size_t)2 * S, 1);
-    std::vector<orbfe_keypoint> hKps((size_t)2 * S);
-    std::vector<int32_t> hNodes((size_t)2 * S, 0), hStarts((size_t)2 * (S + 1), 0), hFeats((size_t)2 * S, 0), hCount(2), hPair(2);
-    memset(hKps.data(), 0, hKps.size() * sizeof(orbfe_keypoint));
-    if (n_kf) memcpy(hDesc.data(), desc_kf, (size_t)n_kf * 32);
-    if (n_f) memcpy(hDesc.data() + (size_t)S * 32, desc_f, (size_t)n_f * 32);
-    if (kps_kf && n_kf) memcpy(hKps.data(), kps_kf, (size_t)n_kf * sizeof(orbfe_keypoint));
-    if (kps_f && n_f) memcpy(hKps.data() + S, kps_f, (size_t)n_f * sizeof(orbfe_keypoint));
-    if (has_map_point && n_kf) memcpy(hMp.data(), has_map_point, (size_t)n_kf);
-    if (has_map_point_f && n_f) memcpy(hMp.data() + S, has_map_point_f, (size_t)n_f);
-    if (nfv_kf > S || nfv_f > S) { orbfe_set_error("feature vector longer than the frame"); return ORBFE_E_INVALID; }
-    if (nfv_kf) {
-        if (fv_starts_kf[nfv_kf] > S) { orbfe_set_error("feature vector longer than the frame"); return ORBFE_E_INVALID; }
-        memcpy(hNodes.data(), fv_nodes_kf, (size_t)nfv_kf * 4); memcpy(hStarts.data(), fv_starts_kf, (size_t)(nfv_kf + 1) * 4);
-        memcpy(hFeats.data(), fv_feats_kf, (size_t)fv_starts_kf[nfv_kf] * 4);
+    if (nfv_kf > S || nfv_f > S || (nfv_kf && fv_starts_kf[nfv_kf] > S) || (nfv_f && fv_starts_f[nfv_f] > S)) {
+        orbfe_set_error("feature vector longer than the frame");
+        return ORBFE_E_INVALID;
     }
-    if (nfv_f) {
-        if (fv_starts_f[nfv_f] > S) { orbfe_set_error("feature vector longer than the frame"); return ORBFE_E_INVALID; }
-        memcpy(hNodes.data() + S, fv_nodes_f, (size_t)nfv_f * 4); memcpy(hStarts.data() + S + 1, fv_starts_f, (size_t)(nfv_f + 1) * 4);
-        memcpy(hFeats.data() + S, fv_feats_f, (size_t)fv_starts_f[nfv_f] * 4);
-    }
-    hCount[0] = nfv_kf; hCount[1] = nfv_f; hPair[0] = 0; hPair[1] = 1;
-    const int32_t hLeft[2] = {-1, n_left_f < 0 ? -1 : n_left_f};
+    /* two frames (0 = keyframe, 1 = frame) in the strided layout of the batch entry point, laid out in the thread's staging block: inputs, then
+     * outputs */
     size_t off = 0;
     auto take = [&](size_t bytes) { const size_t o = off; off += (bytes + 255) & ~(size_t)255; return o; };
-    const size_t oDesc = take(hDesc.size()), oKps = take(hKps.size() * sizeof(orbfe_keypoint)), oMp = take(hMp.size()), oNodes = take(hNodes.size() * 4);
-    const size_t oStarts = take(hStarts.size() * 4), oFeats = take(hFeats.size() * 4), oCount = take(8), oPair = take(8), oMatch = take((size_t)S * 4);
-    const size_t oKf = take((size_t)S * sizeof(orbfe_match)), oNm = take(4), oLeft = take(8);
-    uint8_t* d = nullptr;
-    ORBFE_CUDA(cudaMalloc((void**)&d, off));
-    cudaError_t e = cudaMemcpy(d + oDesc, hDesc.data(), hDesc.size(), cudaMemcpyHostToDevice);
-#define SB_UP(o, v, bytes) if (e == cudaSuccess) e = cudaMemcpy(d + (o), (v), (bytes), cudaMemcpyHostToDevice)
-    SB_UP(oKps, hKps.data(), hKps.size() * sizeof(orbfe_keypoint)); SB_UP(oMp, hMp.data(), hMp.size()); SB_UP(oNodes, hNodes.data(), hNodes.size() * 4);
-    SB_UP(oStarts, hStarts.data(), hStarts.size() * 4); SB_UP(oFeats, hFeats.data(), hFeats.size() * 4); SB_UP(oCount, hCount.data(), 8); SB_UP(oPair, hPair.data(), 8);
-    SB_UP(oLeft, hLeft, 8);
-#undef SB_UP
-    int rc = ORBFE_OK;
+    const size_t oDesc = take((size_t)2 * S * 32), oKps = take((size_t)2 * S * sizeof(orbfe_keypoint)), oMp = take((size_t)2 * S), oNodes = take((size_t)2 * S * 4);
+    const size_t oStarts = take((size_t)2 * (S + 1) * 4), oFeats = take((size_t)2 * S * 4), oCount = take(8), oPair = take(8), oLeft = take(8);
+    const size_t inEnd = off;
+    const size_t oMatch = take((size_t)S * 4), oKf = take((size_t)S * sizeof(orbfe_match)), oNm = take(4);
+    OrbfeStaging ws;
+    int rc = orbfe_thread_staging(device, off, &ws);
+    if (rc != ORBFE_OK) return rc;
+    uint8_t* h = ws.h;
+    uint8_t* d = ws.d;
+    memset(h, 0, inEnd);
+    memset(h + oMp, 1, (size_t)2 * S);
+    orbfe_keypoint* hKps = (orbfe_keypoint*)(h + oKps);
+    int32_t* hNodes = (int32_t*)(h + oNodes); int32_t* hStarts = (int32_t*)(h + oStarts); int32_t* hFeats = (int32_t*)(h + oFeats);
+    if (n_kf) memcpy(h + oDesc, desc_kf, (size_t)n_kf * 32);
+    if (n_f) memcpy(h + oDesc + (size_t)S * 32, desc_f, (size_t)n_f * 32);
+    if (kps_kf && n_kf) memcpy(hKps, kps_kf, (size_t)n_kf * sizeof(orbfe_keypoint));
+    if (kps_f && n_f) memcpy(hKps + S, kps_f, (size_t)n_f * sizeof(orbfe_keypoint));
+    if (has_map_point && n_kf) memcpy(h + oMp, has_map_point, (size_t)n_kf);
+    if (has_map_point_f && n_f) memcpy(h + oMp + S, has_map_point_f, (size_t)n_f);
+    if (nfv_kf) { memcpy(hNodes, fv_nodes_kf, (size_t)nfv_kf * 4); memcpy(hStarts, fv_starts_kf, (size_t)(nfv_kf + 1) * 4); memcpy(hFeats, fv_feats_kf, (size_t)fv_starts_kf[nfv_kf] * 4); }
+    if (nfv_f) { memcpy(hNodes + S, fv_nodes_f, (size_t)nfv_f * 4); memcpy(hStarts + S + 1, fv_starts_f, (size_t)(nfv_f + 1) * 4); memcpy(hFeats + S, fv_feats_f, (size_t)fv_starts_f[nfv_f] * 4); }
+    ((int32_t*)(h + oCount))[0] = nfv_kf; ((int32_t*)(h + oCount))[1] = nfv_f;
+    ((int32_t*)(h + oPair))[0] = 0; ((int32_t*)(h + oPair))[1] = 1;
+    ((int32_t*)(h + oLeft))[0] = -1; ((int32_t*)(h + oLeft))[1] = n_left_f < 0 ? -1 : n_left_f;
+    cudaError_t e = cudaMemcpyAsync(d, h, inEnd, cudaMemcpyHostToDevice, ws.stream);
     if (e == cudaSuccess)
         rc = orbfe_search_by_bow_device(device, 1, S, (const int32_t*)(d + oPair), (const int32_t*)(d + oPair) + 1, d + oDesc, (const orbfe_keypoint*)(d + oKps), S,
                                         (const int32_t*)(d + oNodes), (const int32_t*)(d + oStarts), (const int32_t*)(d + oFeats), (const int32_t*)(d + oCount),
-                                        d + oMp, (const int32_t*)(d + oLeft), th_low, nnratio, check_orientation, kf_kf, (int32_t*)(d + oMatch), (orbfe_match*)(d + oKf), (int32_t*)(d + oNm), nullptr);
-    if (rc == ORBFE_OK && e == cudaSuccess) e = cudaStreamSynchronize(nullptr);   /* the launch above went to the default stream */
-    if (rc == ORBFE_OK && e == cudaSuccess && n_f) e = cudaMemcpy(match_f, d + oMatch, (size_t)n_f * 4, cudaMemcpyDeviceToHost);
-    if (rc == ORBFE_OK && e == cudaSuccess && kf_out && n_kf) e = cudaMemcpy(kf_out, d + oKf, (size_t)n_kf * sizeof(orbfe_match), cudaMemcpyDeviceToHost);
-    if (rc == ORBFE_OK && e == cudaSuccess && nmatches) e = cudaMemcpy(nmatches, d + oNm, 4, cudaMemcpyDeviceToHost);
-    cudaFree(d);
+                                        d + oMp, (const int32_t*)(d + oLeft), th_low, nnratio, check_orientation, kf_kf, (int32_t*)(d + oMatch), (orbfe_match*)(d + oKf),
+                                        (int32_t*)(d + oNm), ws.stream);
+    if (rc == ORBFE_OK && e == cudaSuccess) e = cudaMemcpyAsync(h + inEnd, d + inEnd, off - inEnd, cudaMemcpyDeviceToHost, ws.stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ws.stream);
     if (rc != ORBFE_OK) return rc;
     if (e != cudaSuccess) return orbfe_cuda_fail(e, "search_by_bow");
+    if (n_f) memcpy(match_f, h + oMatch, (size_t)n_f * 4);
+    if (kf_out && n_kf) memcpy(kf_out, h + oKf, (size_t)n_kf * sizeof(orbfe_match));
+    if (nmatches) *nmatches = *(const int32_t*)(h + oNm);
     return ORBFE_OK;
 }
 
@@ -769,18 +795,27 @@ int orbfe_search_for_triangulation_device(int device, int npairs, int max_featur
         !d_scale_factors || !d_level_sigma2 || !d_match_12 || row_stride < 1) { orbfe_set_error("bad argument"); return ORBFE_E_INVALID; }
     if (max_features < 1 || max_features > BOW_MAXF || row_stride > BOW_MAXF) { orbfe_set_error("at most %d features per frame", BOW_MAXF); return ORBFE_E_CAPACITY; }
     if ((uintptr_t)d_desc & 15) { orbfe_set_error("descriptor array must be 16-byte aligned"); return ORBFE_E_INVALID; }
+    if (npairs > 65535) { orbfe_set_error("at most 65535 keyframe pairs per call"); return ORBFE_E_CAPACITY; }
     ORBFE_CUDA(cudaSetDevice(device));
     static_assert(sizeof(TriRig) == sizeof(orbfe_triangulation_rig), "rig layout");
+    /* matching over (split, pair) CTAs — a pair's nodes are dealt out over `split` CTAs, enough of them to cover the SMs twice when there are
+     * few pairs — then the rotation check, one CTA per pair */
+    int sms = 0;
+    ORBFE_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+    const int split = std::min(std::max((2 * sms + npairs - 1) / npairs, 1), 16);
+    const dim3 grid(split, npairs);
+    ORBFE_CUDA(cudaMemsetAsync(d_match_12, 0xFF, (size_t)npairs * row_stride * sizeof(int32_t), (cudaStream_t)stream));
     if (d_rigs)
-        k_search_for_triangulation<true><<<npairs, SB_NT, 0, (cudaStream_t)stream>>>(max_features, d_pair_1, d_pair_2, (const uint4*)d_desc, d_kps, d_u_right, row_stride,
-                                                                                     d_fv_nodes, d_fv_starts, d_fv_feats, d_fv_count, d_has_map_point, d_f12, d_epipole,
-                                                                                     d_scale_factors, d_level_sigma2, th_low, only_stereo ? 1 : 0, coarse ? 1 : 0,
-                                                                                     check_orientation ? 1 : 0, d_match_12, d_nmatches, (const TriRig*)d_rigs);
+        k_search_for_triangulation<true><<<grid, SB_NT, 0, (cudaStream_t)stream>>>(max_features, d_pair_1, d_pair_2, (const uint4*)d_desc, d_kps, d_u_right, row_stride,
+                                                                                   d_fv_nodes, d_fv_starts, d_fv_feats, d_fv_count, d_has_map_point, d_f12, d_epipole,
+                                                                                   d_scale_factors, d_level_sigma2, th_low, only_stereo ? 1 : 0, coarse ? 1 : 0,
+                                                                                   d_match_12, (const TriRig*)d_rigs);
     else
-        k_search_for_triangulation<false><<<npairs, SB_NT, 0, (cudaStream_t)stream>>>(max_features, d_pair_1, d_pair_2, (const uint4*)d_desc, d_kps, d_u_right, row_stride,
-                                                                                      d_fv_nodes, d_fv_starts, d_fv_feats, d_fv_count, d_has_map_point, d_f12, d_epipole,
-                                                                                      d_scale_factors, d_level_sigma2, th_low, only_stereo ? 1 : 0, coarse ? 1 : 0,
-                                                                                      check_orientation ? 1 : 0, d_match_12, d_nmatches, nullptr);
+        k_search_for_triangulation<false><<<grid, SB_NT, 0, (cudaStream_t)stream>>>(max_features, d_pair_1, d_pair_2, (const uint4*)d_desc, d_kps, d_u_right, row_stride,
+                                                                                    d_fv_nodes, d_fv_starts, d_fv_feats, d_fv_count, d_has_map_point, d_f12, d_epipole,
+                                                                                    d_scale_factors, d_level_sigma2, th_low, only_stereo ? 1 : 0, coarse ? 1 : 0,
+                                                                                    d_match_12, nullptr);
+    k_triangulation_rotation<<<npairs, SB_NT, 0, (cudaStream_t)stream>>>(d_pair_1, d_pair_2, d_kps, row_stride, check_orientation ? 1 : 0, d_match_12, d_nmatches);
     ORBFE_CUDA(cudaGetLastError());
     return ORBFE_OK;
 }
@@ -803,50 +838,51 @@ int orbfe_search_for_triangulation(int device, const uint8_t* desc_1, const orbf
         orbfe_set_error("no usable CUDA device %d (found %d); this library has no CPU path", device, ndev);
         return ORBFE_E_CUDA;
     }
-    ORBFE_CUDA(cudaSetDevice(device));
-    std::vector<uint8_t> hDesc((size_t)2 * S * 32, 0), hMp((size_t)2 * S, 0);
-    std::vector<orbfe_keypoint> hKps((size_t)2 * S);
-    std::vector<float> hUr((size_t)2 * S, -1.0f), hPar(9 + 2 + 16 + 16, 0.0f);
-    std::vector<int32_t> hNodes((size_t)2 * S, 0), hStarts((size_t)2 * (S + 1), 0), hFeats((size_t)2 * S, 0), hMisc(4);
-    memset(hKps.data(), 0, hKps.size() * sizeof(orbfe_keypoint));
-    if (n_1) { memcpy(hDesc.data(), desc_1, (size_t)n_1 * 32); memcpy(hKps.data(), kps_1, (size_t)n_1 * sizeof(orbfe_keypoint)); }
-    if (n_2) { memcpy(hDesc.data() + (size_t)S * 32, desc_2, (size_t)n_2 * 32); memcpy(hKps.data() + S, kps_2, (size_t)n_2 * sizeof(orbfe_keypoint)); }
-    if (u_right_1 && n_1) memcpy(hUr.data(), u_right_1, (size_t)n_1 * 4);
-    if (u_right_2 && n_2) memcpy(hUr.data() + S, u_right_2, (size_t)n_2 * 4);
-    if (has_map_point_1 && n_1) memcpy(hMp.data(), has_map_point_1, (size_t)n_1);
-    if (has_map_point_2 && n_2) memcpy(hMp.data() + S, has_map_point_2, (size_t)n_2);
-    if (nfv_1) { memcpy(hNodes.data(), fv_nodes_1, (size_t)nfv_1 * 4); memcpy(hStarts.data(), fv_starts_1, (size_t)(nfv_1 + 1) * 4); memcpy(hFeats.data(), fv_feats_1, (size_t)fv_starts_1[nfv_1] * 4); }
-    if (nfv_2) { memcpy(hNodes.data() + S, fv_nodes_2, (size_t)nfv_2 * 4); memcpy(hStarts.data() + S + 1, fv_starts_2, (size_t)(nfv_2 + 1) * 4); memcpy(hFeats.data() + S, fv_feats_2, (size_t)fv_starts_2[nfv_2] * 4); }
-    memcpy(hPar.data(), f12, 9 * 4); memcpy(hPar.data() + 9, epipole, 2 * 4);
-    memcpy(hPar.data() + 11, scale_factors, (size_t)nlevels * 4); memcpy(hPar.data() + 27, level_sigma2, (size_t)nlevels * 4);
-    hMisc[0] = nfv_1; hMisc[1] = nfv_2; hMisc[2] = 0; hMisc[3] = 1;
+    /* two keyframes (0 and 1) in the strided layout of the batch entry point, laid out in the thread's staging block: inputs, then outputs */
     size_t off = 0;
     auto take = [&](size_t bytes) { const size_t o = off; off += (bytes + 255) & ~(size_t)255; return o; };
-    const size_t oDesc = take(hDesc.size()), oKps = take(hKps.size() * sizeof(orbfe_keypoint)), oUr = take(hUr.size() * 4), oMp = take(hMp.size());
-    const size_t oNodes = take(hNodes.size() * 4), oStarts = take(hStarts.size() * 4), oFeats = take(hFeats.size() * 4), oPar = take(hPar.size() * 4);
-    const size_t oMisc = take(16), oMatch = take((size_t)S * 4), oNm = take(4), oRig = take(sizeof(orbfe_triangulation_rig));
-    uint8_t* d = nullptr;
-    ORBFE_CUDA(cudaMalloc((void**)&d, off));
-    cudaError_t e = cudaMemcpy(d + oDesc, hDesc.data(), hDesc.size(), cudaMemcpyHostToDevice);
-#define ST_UP(o, v, bytes) if (e == cudaSuccess) e = cudaMemcpy(d + (o), (v), (bytes), cudaMemcpyHostToDevice)
-    ST_UP(oKps, hKps.data(), hKps.size() * sizeof(orbfe_keypoint)); ST_UP(oUr, hUr.data(), hUr.size() * 4); ST_UP(oMp, hMp.data(), hMp.size());
-    ST_UP(oNodes, hNodes.data(), hNodes.size() * 4); ST_UP(oStarts, hStarts.data(), hStarts.size() * 4); ST_UP(oFeats, hFeats.data(), hFeats.size() * 4);
-    ST_UP(oPar, hPar.data(), hPar.size() * 4); ST_UP(oMisc, hMisc.data(), 16);
-    if (rig) ST_UP(oRig, rig, sizeof(orbfe_triangulation_rig));
-#undef ST_UP
-    int rc = ORBFE_OK;
+    const size_t oDesc = take((size_t)2 * S * 32), oKps = take((size_t)2 * S * sizeof(orbfe_keypoint)), oUr = take((size_t)2 * S * 4), oMp = take((size_t)2 * S);
+    const size_t oNodes = take((size_t)2 * S * 4), oStarts = take((size_t)2 * (S + 1) * 4), oFeats = take((size_t)2 * S * 4), oPar = take(43 * 4);
+    const size_t oMisc = take(16), oRig = take(sizeof(orbfe_triangulation_rig));
+    const size_t inEnd = off;
+    const size_t oMatch = take((size_t)S * 4), oNm = take(4);
+    OrbfeStaging ws;
+    int rc = orbfe_thread_staging(device, off, &ws);
+    if (rc != ORBFE_OK) return rc;
+    uint8_t* h = ws.h;
+    uint8_t* d = ws.d;
+    memset(h, 0, inEnd);
+    float* hUr = (float*)(h + oUr);
+    for (int i = 0; i < 2 * S; i++) hUr[i] = -1.0f;
+    orbfe_keypoint* hKps = (orbfe_keypoint*)(h + oKps);
+    int32_t* hNodes = (int32_t*)(h + oNodes); int32_t* hStarts = (int32_t*)(h + oStarts); int32_t* hFeats = (int32_t*)(h + oFeats);
+    float* hPar = (float*)(h + oPar);
+    int32_t* hMisc = (int32_t*)(h + oMisc);
+    if (n_1) { memcpy(h + oDesc, desc_1, (size_t)n_1 * 32); memcpy(hKps, kps_1, (size_t)n_1 * sizeof(orbfe_keypoint)); }
+    if (n_2) { memcpy(h + oDesc + (size_t)S * 32, desc_2, (size_t)n_2 * 32); memcpy(hKps + S, kps_2, (size_t)n_2 * sizeof(orbfe_keypoint)); }
+    if (u_right_1 && n_1) memcpy(hUr, u_right_1, (size_t)n_1 * 4);
+    if (u_right_2 && n_2) memcpy(hUr + S, u_right_2, (size_t)n_2 * 4);
+    if (has_map_point_1 && n_1) memcpy(h + oMp, has_map_point_1, (size_t)n_1);
+    if (has_map_point_2 && n_2) memcpy(h + oMp + S, has_map_point_2, (size_t)n_2);
+    if (nfv_1) { memcpy(hNodes, fv_nodes_1, (size_t)nfv_1 * 4); memcpy(hStarts, fv_starts_1, (size_t)(nfv_1 + 1) * 4); memcpy(hFeats, fv_feats_1, (size_t)fv_starts_1[nfv_1] * 4); }
+    if (nfv_2) { memcpy(hNodes + S, fv_nodes_2, (size_t)nfv_2 * 4); memcpy(hStarts + S + 1, fv_starts_2, (size_t)(nfv_2 + 1) * 4); memcpy(hFeats + S, fv_feats_2, (size_t)fv_starts_2[nfv_2] * 4); }
+    memcpy(hPar, f12, 9 * 4); memcpy(hPar + 9, epipole, 2 * 4);
+    memcpy(hPar + 11, scale_factors, (size_t)nlevels * 4); memcpy(hPar + 27, level_sigma2, (size_t)nlevels * 4);
+    hMisc[0] = nfv_1; hMisc[1] = nfv_2; hMisc[2] = 0; hMisc[3] = 1;
+    if (rig) memcpy(h + oRig, rig, sizeof(orbfe_triangulation_rig));
+    cudaError_t e = cudaMemcpyAsync(d, h, inEnd, cudaMemcpyHostToDevice, ws.stream);
     const float* dp = (const float*)(d + oPar);
     if (e == cudaSuccess)
         rc = orbfe_search_for_triangulation_device(device, 1, S, (const int32_t*)(d + oMisc) + 2, (const int32_t*)(d + oMisc) + 3, d + oDesc, (const orbfe_keypoint*)(d + oKps),
                                                    (const float*)(d + oUr), S, (const int32_t*)(d + oNodes), (const int32_t*)(d + oStarts), (const int32_t*)(d + oFeats),
                                                    (const int32_t*)(d + oMisc), d + oMp, dp, dp + 9, dp + 11, dp + 27, th_low, only_stereo, coarse, check_orientation,
-                                                   (int32_t*)(d + oMatch), (int32_t*)(d + oNm), nullptr, rig ? (const orbfe_triangulation_rig*)(d + oRig) : nullptr);
-    if (rc == ORBFE_OK && e == cudaSuccess) e = cudaStreamSynchronize(nullptr);   /* the launch above went to the default stream */
-    if (rc == ORBFE_OK && e == cudaSuccess && n_1) e = cudaMemcpy(match_12, d + oMatch, (size_t)n_1 * 4, cudaMemcpyDeviceToHost);
-    if (rc == ORBFE_OK && e == cudaSuccess && nmatches) e = cudaMemcpy(nmatches, d + oNm, 4, cudaMemcpyDeviceToHost);
-    cudaFree(d);
+                                                   (int32_t*)(d + oMatch), (int32_t*)(d + oNm), ws.stream, rig ? (const orbfe_triangulation_rig*)(d + oRig) : nullptr);
+    if (rc == ORBFE_OK && e == cudaSuccess) e = cudaMemcpyAsync(h + inEnd, d + inEnd, off - inEnd, cudaMemcpyDeviceToHost, ws.stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ws.stream);
     if (rc != ORBFE_OK) return rc;
     if (e != cudaSuccess) return orbfe_cuda_fail(e, "search_for_triangulation");
+    if (n_1) memcpy(match_12, h + oMatch, (size_t)n_1 * 4);
+    if (nmatches) *nmatches = *(const int32_t*)(h + oNm);
     return ORBFE_OK;
 }
 

@@ -74,6 +74,28 @@ __global__ void __launch_bounds__(256) k_to_gray(const uint8_t* __restrict__ src
     dst[i] = (uint8_t)((r * 9798 + c1 * 19235 + b * 3735 + 16384) >> 15);
 }
 
+/* one thread = four adjacent pixels: their 12 or 16 source bytes as three words or one uint4, one word out (src 4- / 16-byte aligned,
+ * dst 4-byte aligned; the caller sends what is left over, or a misaligned batch, to k_to_gray) */
+__device__ __forceinline__ uint32_t gray_of(uint32_t c0, uint32_t c1, uint32_t c2, int rgb) {
+    const uint32_t r = rgb ? c0 : c2, b = rgb ? c2 : c0;
+    return (r * 9798u + c1 * 19235u + b * 3735u + 16384u) >> 15;
+}
+__global__ void __launch_bounds__(256) k_to_gray4(const uint32_t* __restrict__ src, uint32_t* __restrict__ dst, long long ngroups, int channels, int rgb) {
+    const long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= ngroups) return;
+    uint32_t out;
+    if (channels == 3) {
+        const uint32_t w0 = __ldg(src + 3 * g), w1 = __ldg(src + 3 * g + 1), w2 = __ldg(src + 3 * g + 2);
+        out = gray_of(w0 & 255, (w0 >> 8) & 255, (w0 >> 16) & 255, rgb) | gray_of(w0 >> 24, w1 & 255, (w1 >> 8) & 255, rgb) << 8 |
+              gray_of((w1 >> 16) & 255, w1 >> 24, w2 & 255, rgb) << 16 | gray_of((w2 >> 8) & 255, (w2 >> 16) & 255, w2 >> 24, rgb) << 24;
+    } else {
+        const uint4 w = __ldg(reinterpret_cast<const uint4*>(src) + g);
+        out = gray_of(w.x & 255, (w.x >> 8) & 255, (w.x >> 16) & 255, rgb) | gray_of(w.y & 255, (w.y >> 8) & 255, (w.y >> 16) & 255, rgb) << 8 |
+              gray_of(w.z & 255, (w.z >> 8) & 255, (w.z >> 16) & 255, rgb) << 16 | gray_of(w.w & 255, (w.w >> 8) & 255, (w.w >> 16) & 255, rgb) << 24;
+    }
+    dst[g] = out;
+}
+
 struct orbfe_clahe {
     int device, W, H, tilesX, tilesY, tw, th, clipLimit, maxBatch;
     float lutScale, invTw, invTh;
@@ -316,7 +338,15 @@ int orbfe_to_gray_device(int device, const uint8_t* d_src, int channels, int rgb
     if (!d_src || !d_dst || (channels != 3 && channels != 4) || width < 1 || height < 1 || nframes < 1) { orbfe_set_error("bad argument"); return ORBFE_E_INVALID; }
     ORBFE_CUDA(cudaSetDevice(device));
     const long long npix = (long long)width * height * nframes;
-    k_to_gray<<<(unsigned)((npix + 255) / 256), 256, 0, (cudaStream_t)stream>>>(d_src, d_dst, npix, channels, rgb_order ? 1 : 0);
+    long long done = 0;
+    if (((uintptr_t)d_src & (channels == 4 ? 15 : 3)) == 0 && ((uintptr_t)d_dst & 3) == 0 && npix >= 4) {
+        const long long ngroups = npix / 4;
+        k_to_gray4<<<(unsigned)((ngroups + 255) / 256), 256, 0, (cudaStream_t)stream>>>((const uint32_t*)d_src, (uint32_t*)d_dst, ngroups, channels, rgb_order ? 1 : 0);
+        ORBFE_CUDA(cudaGetLastError());
+        done = ngroups * 4;
+    }
+    if (done < npix)
+        k_to_gray<<<(unsigned)((npix - done + 255) / 256), 256, 0, (cudaStream_t)stream>>>(d_src + done * channels, d_dst + done, npix - done, channels, rgb_order ? 1 : 0);
     ORBFE_CUDA(cudaGetLastError());
     return ORBFE_OK;
 }

@@ -9,6 +9,7 @@
 
 #include <algorithm>
 #include <new>
+#include <vector>
 
 #include "orbfe_internal.h"
 
@@ -32,6 +33,50 @@ void orbfe_set_error(const char* fmt, ...) {
 int orbfe_cuda_fail(cudaError_t e, const char* what) {
     orbfe_set_error("CUDA error %d (%s) in %s", (int)e, cudaGetErrorString(e), what);
     return ORBFE_E_CUDA;
+}
+
+namespace {
+struct StagingSlot { int device; uint8_t* d; uint8_t* h; size_t cap; cudaStream_t stream; };
+struct ThreadStaging {
+    std::vector<StagingSlot> slots;
+    void release() {
+        for (StagingSlot& s : slots) {
+            if (cudaSetDevice(s.device) != cudaSuccess) continue;
+            if (s.stream) { cudaStreamSynchronize(s.stream); cudaStreamDestroy(s.stream); }
+            cudaFree(s.d);
+            cudaFreeHost(s.h);
+        }
+        slots.clear();
+    }
+    ~ThreadStaging() { release(); }
+};
+thread_local ThreadStaging t_staging;
+}  // namespace
+
+int orbfe_thread_staging(int device, size_t bytes, OrbfeStaging* out) {
+    ORBFE_CUDA(cudaSetDevice(device));
+    StagingSlot* s = nullptr;
+    for (StagingSlot& x : t_staging.slots)
+        if (x.device == device) s = &x;
+    if (!s) {
+        cudaStream_t st = nullptr;
+        ORBFE_CUDA(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+        t_staging.slots.push_back(StagingSlot{device, nullptr, nullptr, 0, st});
+        s = &t_staging.slots.back();
+    }
+    if (s->cap < bytes) {
+        ORBFE_CUDA(cudaStreamSynchronize(s->stream));
+        cudaFree(s->d); cudaFreeHost(s->h);
+        s->d = s->h = nullptr; s->cap = 0;
+        const size_t want = std::max(bytes + bytes / 2, (size_t)1 << 20);
+        void* d = nullptr; void* h = nullptr;
+        ORBFE_CUDA(cudaMalloc(&d, want));
+        const cudaError_t e = cudaMallocHost(&h, want);
+        if (e != cudaSuccess) { cudaFree(d); return orbfe_cuda_fail(e, "cudaMallocHost (thread staging)"); }
+        s->d = (uint8_t*)d; s->h = (uint8_t*)h; s->cap = want;
+    }
+    out->d = s->d; out->h = s->h; out->stream = s->stream;
+    return ORBFE_OK;
 }
 
 static const int8_t kPattern[1024] = {
@@ -98,6 +143,8 @@ static int dev_alloc(orbfe_extractor* ex, T** p, size_t count) {
 extern "C" {
 
 const char* orbfe_last_error(void) { return g_err; }
+
+void orbfe_thread_release(void) { t_staging.release(); }
 const char* orbfe_version(void) { return "orbfe 0.1 (sm_100a)"; }
 
 int orbfe_device_count(void) {

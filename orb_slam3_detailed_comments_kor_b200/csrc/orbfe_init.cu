@@ -314,40 +314,37 @@ int orbfe_search_for_initialization(int device, const orbfe_keypoint* kps1, cons
         orbfe_set_error("no usable CUDA device %d (found %d); this library has no CPU path", device, ndev);
         return ORBFE_E_CUDA;
     }
-    ORBFE_CUDA(cudaSetDevice(device));
+    /* the thread's staging block: inputs | vbPrevMatched (in and out) | outputs */
     size_t off = 0;
     auto take = [&](size_t bytes) { const size_t o = off; off += (bytes + 255) & ~(size_t)255; return o; };
     const size_t oK1 = take((size_t)n1 * sizeof(orbfe_keypoint)), oD1 = take((size_t)n1 * 32), oK2 = take((size_t)n2 * sizeof(orbfe_keypoint)), oD2 = take((size_t)n2 * 32);
-    const size_t oPrev = take((size_t)n1 * 8), oM = take((size_t)n1 * 4), oGrid = take(sizeof(orbfe_frame_grid)), oOff = take(6 * sizeof(int32_t));
-    uint8_t* d = nullptr;
-    ORBFE_CUDA(cudaMalloc((void**)&d, off));
-    cudaStream_t st = nullptr;
-    const int32_t offs[6] = {0, n1, 0, n2, 0, 0};
-    int32_t nm = 0;
-    cudaError_t e = cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking);
-#define SI_UP(dst, src, bytes) if (e == cudaSuccess && (bytes) > 0) e = cudaMemcpyAsync(d + (dst), (src), (bytes), cudaMemcpyHostToDevice, st)
-    SI_UP(oK1, kps1, (size_t)n1 * sizeof(orbfe_keypoint));
-    SI_UP(oD1, desc1, (size_t)n1 * 32);
-    SI_UP(oK2, kps2, (size_t)n2 * sizeof(orbfe_keypoint));
-    SI_UP(oD2, desc2, (size_t)n2 * 32);
-    SI_UP(oPrev, prev_matched, (size_t)n1 * 8);
-    SI_UP(oGrid, grid, sizeof(orbfe_frame_grid));
-    SI_UP(oOff, offs, sizeof(offs));
-#undef SI_UP
-    int rc = ORBFE_OK;
+    const size_t oGrid = take(sizeof(orbfe_frame_grid)), oOff = take(4 * sizeof(int32_t)), oPrev = take((size_t)n1 * 8);
+    const size_t inEnd = off;
+    const size_t oM = take((size_t)n1 * 4), oRes = take(2 * sizeof(int32_t));
+    OrbfeStaging ws;
+    int rc = orbfe_thread_staging(device, off, &ws);
+    if (rc != ORBFE_OK) return rc;
+    uint8_t* h = ws.h;
+    uint8_t* d = ws.d;
+    memcpy(h + oK1, kps1, (size_t)n1 * sizeof(orbfe_keypoint));
+    memcpy(h + oD1, desc1, (size_t)n1 * 32);
+    if (n2) { memcpy(h + oK2, kps2, (size_t)n2 * sizeof(orbfe_keypoint)); memcpy(h + oD2, desc2, (size_t)n2 * 32); }
+    memcpy(h + oGrid, grid, sizeof(orbfe_frame_grid));
+    const int32_t offs[4] = {0, n1, 0, n2};
+    memcpy(h + oOff, offs, sizeof(offs));
+    memcpy(h + oPrev, prev_matched, (size_t)n1 * 8);
+    cudaError_t e = cudaMemcpyAsync(d, h, inEnd, cudaMemcpyHostToDevice, ws.stream);
     if (e == cudaSuccess)
         rc = orbfe_search_for_initialization_device(device, 1, (const orbfe_keypoint*)(d + oK1), d + oD1, (const int32_t*)(d + oOff), (const orbfe_keypoint*)(d + oK2),
                                                     d + oD2, (const int32_t*)(d + oOff) + 2, (const orbfe_frame_grid*)(d + oGrid), (float*)(d + oPrev), window, nnratio,
-                                                    check_orientation, th_low, (int32_t*)(d + oM), (int32_t*)(d + oOff) + 4, (int32_t*)(d + oOff) + 5, st);
-    if (rc == ORBFE_OK && e == cudaSuccess) e = cudaMemcpyAsync(matches12, d + oM, (size_t)n1 * 4, cudaMemcpyDeviceToHost, st);
-    if (rc == ORBFE_OK && e == cudaSuccess) e = cudaMemcpyAsync(prev_matched, d + oPrev, (size_t)n1 * 8, cudaMemcpyDeviceToHost, st);
-    if (rc == ORBFE_OK && e == cudaSuccess) e = cudaMemcpyAsync(&nm, d + oOff + 4 * sizeof(int32_t), sizeof(int32_t), cudaMemcpyDeviceToHost, st);
-    if (rc == ORBFE_OK && e == cudaSuccess) e = cudaStreamSynchronize(st);
-    if (st) cudaStreamDestroy(st);
-    cudaFree(d);
+                                                    check_orientation, th_low, (int32_t*)(d + oM), (int32_t*)(d + oRes), (int32_t*)(d + oRes) + 1, ws.stream);
+    if (rc == ORBFE_OK && e == cudaSuccess) e = cudaMemcpyAsync(h + oPrev, d + oPrev, off - oPrev, cudaMemcpyDeviceToHost, ws.stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ws.stream);
     if (rc != ORBFE_OK) return rc;
     if (e != cudaSuccess) return orbfe_cuda_fail(e, "search_for_initialization");
-    if (nmatches) *nmatches = nm;
+    memcpy(matches12, h + oM, (size_t)n1 * 4);
+    memcpy(prev_matched, h + oPrev, (size_t)n1 * 8);
+    if (nmatches) *nmatches = *(const int32_t*)(h + oRes);
     return ORBFE_OK;
 }
 

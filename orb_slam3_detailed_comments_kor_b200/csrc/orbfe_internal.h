@@ -185,4 +185,12 @@ int orbfe_cuda_fail(cudaError_t e, const char* what);
         if (e__ != cudaSuccess) return orbfe_cuda_fail(e__, #call); \
     } while (0)
 
+/* The calling thread's staging block on a device: pinned host memory and device memory of the same size, and a stream.  It grows when a
+ * call needs more and stays for the life of the thread (or until orbfe_thread_release), so that a one-frame host entry point — the
+ * matchers behind the shims, called once per frame or keyframe pair — costs one copy up, its kernels and one copy down rather than an
+ * allocation, a stream and a dozen pageable copies per call. */
+struct OrbfeStaging { uint8_t* d; uint8_t* h; cudaStream_t stream; };
+#define ORBFE_STAGING_MAX ((size_t)32 << 20)   /* entry points whose size is open-ended stage through it up to here, beyond it they allocate per call */
+int orbfe_thread_staging(int device, size_t bytes, OrbfeStaging* out);
+
 #endif

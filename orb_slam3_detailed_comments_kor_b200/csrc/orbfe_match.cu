@@ -888,6 +888,24 @@ int orbfe_knn2_ratio(int device, const uint8_t* q, int nq, const uint8_t* t, int
 int orbfe_descriptor_distances(int device, const uint8_t* a, const uint8_t* b, int64_t n, int32_t* out) {
     if (!a || !b || !out || n < 1) { orbfe_set_error("bad argument"); return ORBFE_E_INVALID; }
     ORBFE_CUDA(cudaSetDevice(device));
+    const size_t bIn = ((size_t)n * 32 + 255) & ~(size_t)255;
+    if (2 * bIn + (size_t)n * 4 <= ORBFE_STAGING_MAX) {                          /* the usual size: through the thread's staging block */
+        OrbfeStaging ws;
+        const int rc = orbfe_thread_staging(device, 2 * bIn + (size_t)n * 4, &ws);
+        if (rc != ORBFE_OK) return rc;
+        memcpy(ws.h, a, (size_t)n * 32);
+        memcpy(ws.h + bIn, b, (size_t)n * 32);
+        cudaError_t e = cudaMemcpyAsync(ws.d, ws.h, 2 * bIn, cudaMemcpyHostToDevice, ws.stream);
+        if (e == cudaSuccess) {
+            k_pair_distances<<<(unsigned)((n + 255) / 256), 256, 0, ws.stream>>>((const uint4*)ws.d, (const uint4*)(ws.d + bIn), n, (int*)(ws.d + 2 * bIn));
+            e = cudaGetLastError();
+        }
+        if (e == cudaSuccess) e = cudaMemcpyAsync(ws.h + 2 * bIn, ws.d + 2 * bIn, (size_t)n * 4, cudaMemcpyDeviceToHost, ws.stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(ws.stream);
+        if (e != cudaSuccess) return orbfe_cuda_fail(e, "descriptor_distances");
+        memcpy(out, ws.h + 2 * bIn, (size_t)n * 4);
+        return ORBFE_OK;
+    }
     uint8_t *da = nullptr, *db = nullptr;
     int* dout = nullptr;
     cudaError_t e = cudaMalloc((void**)&da, (size_t)n * 32);
@@ -927,6 +945,24 @@ int orbfe_distinctive_descriptors(int device, const uint8_t* desc, const int32_t
     ORBFE_CUDA(cudaSetDevice(device));
     const size_t rows = (size_t)offsets[npoints], bDesc = (rows * 32 + 255) & ~(size_t)255, bOff = ((size_t)(npoints + 1) * 4 + 255) & ~(size_t)255;
     const size_t bOut = ((size_t)npoints * 4 + 255) & ~(size_t)255;
+    if (bDesc + bOff + 2 * bOut <= ORBFE_STAGING_MAX) {                           /* the usual size: through the thread's staging block */
+        OrbfeStaging ws;
+        int rc = orbfe_thread_staging(device, bDesc + bOff + 2 * bOut, &ws);
+        if (rc != ORBFE_OK) return rc;
+        if (rows) memcpy(ws.h, desc, rows * 32);
+        memcpy(ws.h + bDesc, offsets, (size_t)(npoints + 1) * 4);
+        cudaError_t e = cudaMemcpyAsync(ws.d, ws.h, bDesc + bOff, cudaMemcpyHostToDevice, ws.stream);
+        if (e == cudaSuccess)
+            rc = orbfe_distinctive_descriptors_device(device, ws.d, (const int32_t*)(ws.d + bDesc), npoints, (int32_t*)(ws.d + bDesc + bOff),
+                                                      (int32_t*)(ws.d + bDesc + bOff + bOut), ws.stream);
+        if (rc == ORBFE_OK && e == cudaSuccess) e = cudaMemcpyAsync(ws.h + bDesc + bOff, ws.d + bDesc + bOff, 2 * bOut, cudaMemcpyDeviceToHost, ws.stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(ws.stream);
+        if (rc != ORBFE_OK) return rc;
+        if (e != cudaSuccess) return orbfe_cuda_fail(e, "distinctive_descriptors");
+        memcpy(best_idx, ws.h + bDesc + bOff, (size_t)npoints * 4);
+        if (best_median) memcpy(best_median, ws.h + bDesc + bOff + bOut, (size_t)npoints * 4);
+        return ORBFE_OK;
+    }
     uint8_t* d = nullptr;
     ORBFE_CUDA(cudaMalloc((void**)&d, bDesc + bOff + 2 * bOut + 256));
     cudaError_t e = rows ? cudaMemcpy(d, desc, rows * 32, cudaMemcpyHostToDevice) : cudaSuccess;

@@ -428,47 +428,44 @@ int orbfe_search_by_projection(int device, const orbfe_keypoint* kps, const uint
         orbfe_set_error("no usable CUDA device %d (found %d); this library has no CPU path", device, ndev);
         return ORBFE_E_CUDA;
     }
-    ORBFE_CUDA(cudaSetDevice(device));
-    /* one staging block: [kps | desc | qdesc | queries | out | uRight | partner | taken | grid | offsets | nLeft] */
+    for (int i = 0; i < nq; i++)
+        if ((queries[i].flags & ORBFE_PQ_ERROR_GATE) && !inv_level_sigma2) { orbfe_set_error("ORBFE_PQ_ERROR_GATE needs inv_level_sigma2"); return ORBFE_E_INVALID; }
+    /* the thread's staging block: [kps | desc | qdesc | queries | uRight | partner | grid | offsets | sigma] [taken: in and out] [out] */
     size_t off = 0;
     auto take = [&](size_t bytes) { const size_t o = off; off += (bytes + 255) & ~(size_t)255; return o; };
     const size_t oKps = take((size_t)n * sizeof(orbfe_keypoint)), oDesc = take((size_t)n * 32), oQd = take((size_t)nq * 32);
-    const size_t oQ = take((size_t)nq * sizeof(orbfe_proj_query)), oOut = take((size_t)nq * sizeof(orbfe_proj_match));
-    const size_t oUr = take((size_t)n * 4), oPt = take((size_t)n * 4), oTk = take((size_t)n), oGrid = take(sizeof(orbfe_frame_grid)), oOff = take(5 * sizeof(int32_t));
-    const size_t oSig = take(16 * sizeof(float));
-    for (int i = 0; i < nq; i++)
-        if ((queries[i].flags & ORBFE_PQ_ERROR_GATE) && !inv_level_sigma2) { orbfe_set_error("ORBFE_PQ_ERROR_GATE needs inv_level_sigma2"); return ORBFE_E_INVALID; }
-    uint8_t* d = nullptr;
-    ORBFE_CUDA(cudaMalloc((void**)&d, off));
-    cudaStream_t st = nullptr;
+    const size_t oQ = take((size_t)nq * sizeof(orbfe_proj_query)), oUr = take((size_t)n * 4), oPt = take((size_t)n * 4), oGrid = take(sizeof(orbfe_frame_grid));
+    const size_t oOff = take(5 * sizeof(int32_t)), oSig = take(16 * sizeof(float)), oTk = take((size_t)n);
+    const size_t inEnd = off;
+    const size_t oOut = take((size_t)nq * sizeof(orbfe_proj_match));
+    OrbfeStaging ws;
+    int rc = orbfe_thread_staging(device, off, &ws);
+    if (rc != ORBFE_OK) return rc;
+    uint8_t* h = ws.h;
+    uint8_t* d = ws.d;
     const int32_t offs[5] = {0, n, 0, nq, n_left};
-    cudaError_t e = cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking);
-#define PJ_UP(dst, src, bytes) if (e == cudaSuccess && (bytes) > 0) e = cudaMemcpyAsync(d + (dst), (src), (bytes), cudaMemcpyHostToDevice, st)
-    PJ_UP(oKps, kps, (size_t)n * sizeof(orbfe_keypoint));
-    PJ_UP(oDesc, desc, (size_t)n * 32);
-    PJ_UP(oQd, qdesc, (size_t)nq * 32);
-    PJ_UP(oQ, queries, (size_t)nq * sizeof(orbfe_proj_query));
-    if (u_right) PJ_UP(oUr, u_right, (size_t)n * 4);
-    if (partner) PJ_UP(oPt, partner, (size_t)n * 4);
-    if (taken) PJ_UP(oTk, taken, (size_t)n);
-    PJ_UP(oGrid, grid, sizeof(orbfe_frame_grid));
-    PJ_UP(oOff, offs, sizeof(offs));
-    if (inv_level_sigma2) PJ_UP(oSig, inv_level_sigma2, 16 * sizeof(float));
-#undef PJ_UP
-    int rc = ORBFE_OK;
+    if (n) { memcpy(h + oKps, kps, (size_t)n * sizeof(orbfe_keypoint)); memcpy(h + oDesc, desc, (size_t)n * 32); }
+    memcpy(h + oQd, qdesc, (size_t)nq * 32);
+    memcpy(h + oQ, queries, (size_t)nq * sizeof(orbfe_proj_query));
+    if (u_right && n) memcpy(h + oUr, u_right, (size_t)n * 4);
+    if (partner && n) memcpy(h + oPt, partner, (size_t)n * 4);
+    if (taken && n) memcpy(h + oTk, taken, (size_t)n);
+    memcpy(h + oGrid, grid, sizeof(orbfe_frame_grid));
+    memcpy(h + oOff, offs, sizeof(offs));
+    if (inv_level_sigma2) memcpy(h + oSig, inv_level_sigma2, 16 * sizeof(float));
+    cudaError_t e = cudaMemcpyAsync(d, h, inEnd, cudaMemcpyHostToDevice, ws.stream);
     if (e == cudaSuccess)
         rc = orbfe_search_by_projection_device(device, 1, PJ_MAXKP, (const orbfe_keypoint*)(d + oKps), d + oDesc, (const int32_t*)(d + oOff),
                                                (const int32_t*)(d + oOff) + 4, u_right ? (const float*)(d + oUr) : nullptr,
                                                partner ? (const int32_t*)(d + oPt) : nullptr, taken ? d + oTk : nullptr, (const orbfe_frame_grid*)(d + oGrid),
                                                (const orbfe_proj_query*)(d + oQ), d + oQd, (const int32_t*)(d + oOff) + 2, th_high, nnratio, check_orientation,
-                                               inv_level_sigma2 ? (const float*)(d + oSig) : nullptr, (orbfe_proj_match*)(d + oOut), taken ? d + oTk : nullptr, st);
-    if (rc == ORBFE_OK && e == cudaSuccess) e = cudaMemcpyAsync(out, d + oOut, (size_t)nq * sizeof(orbfe_proj_match), cudaMemcpyDeviceToHost, st);
-    if (rc == ORBFE_OK && e == cudaSuccess && taken && n > 0) e = cudaMemcpyAsync(taken, d + oTk, (size_t)n, cudaMemcpyDeviceToHost, st);
-    if (rc == ORBFE_OK && e == cudaSuccess) e = cudaStreamSynchronize(st);
-    if (st) cudaStreamDestroy(st);
-    cudaFree(d);
+                                               inv_level_sigma2 ? (const float*)(d + oSig) : nullptr, (orbfe_proj_match*)(d + oOut), taken ? d + oTk : nullptr, ws.stream);
+    if (rc == ORBFE_OK && e == cudaSuccess) e = cudaMemcpyAsync(h + oTk, d + oTk, off - oTk, cudaMemcpyDeviceToHost, ws.stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ws.stream);
     if (rc != ORBFE_OK) return rc;
     if (e != cudaSuccess) return orbfe_cuda_fail(e, "search_by_projection");
+    memcpy(out, h + oOut, (size_t)nq * sizeof(orbfe_proj_match));
+    if (taken && n > 0) memcpy(taken, h + oTk, (size_t)n);
     if (nmatches) {
         int c = 0;
         for (int i = 0; i < nq; i++)

@@ -103,6 +103,19 @@ def test_gpu_gray_matches_oracle_and_cv2():
         out = d_dst.cpu().numpy()
         assert np.array_equal(out[0], g[key]), key
         assert np.array_equal(out[1], O.to_gray(batch[1], rgb)), key
+        # a pixel count that is not a multiple of four (the word kernel plus the byte kernel for the rest), and pointers off the word grid
+        odd = np.ascontiguousarray(src[:7, :9])
+        flat = torch.zeros(odd.size + 8, dtype=torch.uint8, device="cuda")
+        o_dst = torch.zeros(7 * 9 + 8, dtype=torch.uint8, device="cuda")
+        for shift_src, shift_dst in ((0, 0), (1, 0), (0, 2), (3, 1)):
+            flat[shift_src:shift_src + odd.size] = torch.from_numpy(odd.reshape(-1)).cuda()
+            o_dst.zero_()
+            torch.cuda.synchronize()
+            to_gray_device(flat.data_ptr() + shift_src, ch, rgb, 9, 7, 1, o_dst.data_ptr() + shift_dst, stream=st.cuda_stream)
+            st.synchronize()
+            got = o_dst.cpu().numpy()
+            assert np.array_equal(got[shift_dst:shift_dst + 63].reshape(7, 9), O.to_gray(odd, rgb)), (key, shift_src, shift_dst)
+            assert not got[:shift_dst].any() and not got[shift_dst + 63:].any()
 
 
 @pytest.mark.gpu
