@@ -206,6 +206,7 @@ __global__ void __launch_bounds__(BOW_NT) k_bow_assemble(const int* __restrict__
  * the stamp of an earlier unresolved query.  Queries of different nodes never share a candidate, and inside a node only queries that
  * compete for a feature both could take wait for each other. */
 #define SB_NT 256
+#define SBW_NT 1024     /* SearchByBoW: one CTA per pair, and a single pair (one Tracking call) should not wait on 8 warps */
 #define SB_FREE 0xFFFFu      /* takenBy: nobody */
 #define SB_PENDING 0x8000u   /* takenBy: taken in the running round, visible from the next one */
 struct SbSmem {
@@ -216,7 +217,7 @@ struct SbSmem {
     int rot[32];
 };
 
-__global__ void __launch_bounds__(SB_NT) k_search_by_bow(int maxF, const int* __restrict__ pairKf, const int* __restrict__ pairF, const uint4* __restrict__ desc,
+__global__ void __launch_bounds__(SBW_NT) k_search_by_bow(int maxF, const int* __restrict__ pairKf, const int* __restrict__ pairF, const uint4* __restrict__ desc,
                                                          const orbfe_keypoint* __restrict__ kps, int rowStride, const int* __restrict__ fvNodes,
                                                          const int* __restrict__ fvStarts, const int* __restrict__ fvFeats, const int* __restrict__ fvCount,
                                                          const uint8_t* __restrict__ hasMp, const int* __restrict__ nLeftAll, int thLow, float nnratio,
@@ -234,13 +235,13 @@ __global__ void __launch_bounds__(SB_NT) k_search_by_bow(int maxF, const int* __
     int* mF = matchF + (size_t)pr * rowStride;
     orbfe_match* ko = kfOut ? kfOut + (size_t)pr * rowStride : nullptr;
     uint8_t* stateB = reinterpret_cast<uint8_t*>(s.state);
-    for (int i = tid; i < rowStride; i += SB_NT) { mF[i] = -1; if (ko) { orbfe_match m; m.best1 = 256; m.best2 = 256; m.idx = -1; m.accepted = 0; ko[i] = m; } }
-    for (int i = tid; i < BOW_MAXF / 4; i += SB_NT) s.state[i] = 0;
+    for (int i = tid; i < rowStride; i += SBW_NT) { mF[i] = -1; if (ko) { orbfe_match m; m.best1 = 256; m.best2 = 256; m.idx = -1; m.accepted = 0; ko[i] = m; } }
+    for (int i = tid; i < BOW_MAXF / 4; i += SBW_NT) s.state[i] = 0;
     /* keyframe-keyframe variant: rows of the second keyframe without a map point are never candidates (:886-892) */
-    for (int i = tid; i < BOW_MAXF; i += SB_NT) s.takenBy[i] = (kfkf && hasMp && i < rowStride && !hasMp[(size_t)b * rowStride + i]) ? 0 : SB_FREE;
+    for (int i = tid; i < BOW_MAXF; i += SBW_NT) s.takenBy[i] = (kfkf && hasMp && i < rowStride && !hasMp[(size_t)b * rowStride + i]) ? 0 : SB_FREE;
     __syncthreads();
     /* the node of every query, and that node's run in the frame's feature vector (the lockstep walk of :290-420 is a merge join) */
-    for (int e = tid; e < nnA; e += SB_NT) {
+    for (int e = tid; e < nnA; e += SBW_NT) {
         const int node = nodesA[e];
         int lo = 0, hi = nnB;
         while (lo < hi) { const int mid = (lo + hi) >> 1; if (nodesB[mid] < node) lo = mid + 1; else hi = mid; }
@@ -260,35 +261,45 @@ __global__ void __launch_bounds__(SB_NT) k_search_by_bow(int maxF, const int* __
      * queries of a node would resolve one per round even when nothing matches. */
 #define SB_TAKEN_FOR(row, q) ((unsigned)s.takenBy[row] <= (unsigned)(q))   /* stored q' + 1 <= q  <=>  q' < q; pending and free values are >= 0x8000 */
     for (;;) {
-        for (int i = tid; i < maxF; i += SB_NT) {
+        for (int i = tid; i < maxF; i += SBW_NT) {
             s.owner[i] = INT_MAX;
             const unsigned v = s.takenBy[i];
             if ((v & SB_PENDING) && v != SB_FREE) s.takenBy[i] = (uint16_t)(v & ~SB_PENDING);
         }
         __syncthreads();
-        for (int q = tid; q < nq; q += SB_NT) {
+        /* the candidate loops go four rows at a time: the row numbers, then the four descriptors, are loaded before any is used, so that a
+         * thread waits for memory once per four candidates rather than twice per candidate */
+#define SB_SCAN(BODY)                                                                                                  \
+        for (int j = rg & 0xFFFF, j1 = (int)(rg >> 16); j < j1; j += 4) {                                                  \
+            int rows4[4]; uint4 da4[4], db4[4];                                                                            \
+            _Pragma("unroll") for (int k = 0; k < 4; k++) rows4[k] = featsB[min(j + k, j1 - 1)];                           \
+            _Pragma("unroll") for (int k = 0; k < 4; k++) { da4[k] = __ldg(descB + 2 * rows4[k]); db4[k] = __ldg(descB + 2 * rows4[k] + 1); } \
+            _Pragma("unroll") for (int k = 0; k < 4; k++) {                                                                \
+                if (j + k >= j1) break;                                                                                    \
+                const int row = rows4[k];                                                                                  \
+                if (SB_TAKEN_FOR(row, q)) continue;               /* if(vpMapPointMatches[realIdxF]) continue; */          \
+                const int dist = bow_ham(qa, qb, da4[k], db4[k]);                                                          \
+                BODY                                                                                                       \
+            }                                                                                                              \
+        }
+        for (int q = tid; q < nq; q += SBW_NT) {
             if (stateB[q]) continue;
             const uint32_t rg = s.range[q];
             const int rowA = featsA[q];
             const uint4 qa = __ldg(descA + 2 * rowA), qb = __ldg(descA + 2 * rowA + 1);
-            for (int j = rg & 0xFFFF; j < (int)(rg >> 16); j++) {
-                const int row = featsB[j];
-                if (!SB_TAKEN_FOR(row, q) && bow_ham(qa, qb, __ldg(descB + 2 * row), __ldg(descB + 2 * row + 1)) <= thLow) atomicMin(&s.owner[row], q);
-            }
+            SB_SCAN(if (dist <= thLow) atomicMin(&s.owner[row], q);)
         }
         __syncthreads();
         int pending = 0;
-        for (int q = tid; q < nq; q += SB_NT) {
+        for (int q = tid; q < nq; q += SBW_NT) {
             if (stateB[q]) continue;
             const uint32_t rg = s.range[q];
             const int rowA = featsA[q];
             const uint4 qa = __ldg(descA + 2 * rowA), qb = __ldg(descA + 2 * rowA + 1);
             int best1 = 256, best2 = 256, bestIdx = -1;
             int best1R = 256, best2R = 256, bestIdxR = -1;        /* fisheye rig: the frame's right-camera rows compete separately (:330-358) */
-            for (int j = rg & 0xFFFF; j < (int)(rg >> 16); j++) {
-                const int row = featsB[j];
-                if (SB_TAKEN_FOR(row, q)) continue;               /* if(vpMapPointMatches[realIdxF]) continue; */
-                const int dist = bow_ham(qa, qb, __ldg(descB + 2 * row), __ldg(descB + 2 * row + 1));
+            int foreign = 257;                                    /* the closest candidate that carries the stamp of an earlier unresolved query */
+            SB_SCAN(
                 if (nLeftF < 0 || row < nLeftF) {
                     if (dist < best1) { best2 = best1; best1 = dist; bestIdx = row; }
                     else if (dist < best2) best2 = dist;
@@ -296,15 +307,9 @@ __global__ void __launch_bounds__(SB_NT) k_search_by_bow(int maxF, const int* __
                     if (dist < best1R) { best2R = best1R; best1R = dist; bestIdxR = row; }
                     else if (dist < best2R) best2R = dist;
                 }
-            }
+                if (s.owner[row] < q) foreign = min(foreign, dist);)
             const int reach = nLeftF < 0 ? best2 : max(best2, best2R);
-            bool blocked = false;
-            for (int j = rg & 0xFFFF; j < (int)(rg >> 16) && !blocked; j++) {
-                const int row = featsB[j];
-                if (SB_TAKEN_FOR(row, q) || s.owner[row] >= q) continue;
-                if (bow_ham(qa, qb, __ldg(descB + 2 * row), __ldg(descB + 2 * row + 1)) <= reach) blocked = true;
-            }
-            if (blocked) { pending++; continue; }
+            if (foreign <= reach) { pending++; continue; }
             const bool th1 = bestIdx >= 0 && (kfkf ? best1 < thLow : best1 <= thLow);
             const bool ok = th1 && (float)best1 < nnratio * (float)best2;
             /* :388-416: inside `if(bestDist1<=TH_LOW)`, the right-camera best is taken whenever it is <= TH_LOW (`|| true`) */
@@ -316,6 +321,7 @@ __global__ void __launch_bounds__(SB_NT) k_search_by_bow(int maxF, const int* __
         }
         if (__syncthreads_count(pending) == 0) break;
     }
+#undef SB_SCAN
 #undef SB_TAKEN_FOR
     /* rotation consistency (:368-384, 440-458) */
     if (checkOri) {
@@ -323,7 +329,7 @@ __global__ void __launch_bounds__(SB_NT) k_search_by_bow(int maxF, const int* __
         const orbfe_keypoint* kA = kps + (size_t)a * rowStride; const orbfe_keypoint* kB = kps + (size_t)b * rowStride;
         if (tid < 32) s.rot[tid] = 0;
         __syncthreads();
-        for (int i = tid; i < rowStride; i += SB_NT) {
+        for (int i = tid; i < rowStride; i += SBW_NT) {
             const int ra = mF[i];
             if (ra < 0) continue;
             float rot = __ldg(&kA[ra].angle) - __ldg(&kB[i].angle);
@@ -347,7 +353,7 @@ __global__ void __launch_bounds__(SB_NT) k_search_by_bow(int maxF, const int* __
         }
         __syncthreads();
         const int ind1 = s.rot[30], ind2 = (int)(signed char)(s.rot[31] & 0xFF), ind3 = (int)(signed char)((s.rot[31] >> 8) & 0xFF);
-        for (int i = tid; i < rowStride; i += SB_NT) {
+        for (int i = tid; i < rowStride; i += SBW_NT) {
             const int ra = mF[i];
             if (ra < 0) continue;
             float rot = __ldg(&kA[ra].angle) - __ldg(&kB[i].angle);
@@ -362,7 +368,7 @@ __global__ void __launch_bounds__(SB_NT) k_search_by_bow(int maxF, const int* __
         __syncthreads();
     }
     int cnt = 0;
-    for (int i = tid; i < rowStride; i += SB_NT) cnt += mF[i] >= 0 ? 1 : 0;
+    for (int i = tid; i < rowStride; i += SBW_NT) cnt += mF[i] >= 0 ? 1 : 0;
 #pragma unroll
     for (int o = 16; o; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
     __shared__ int s_total;
@@ -714,7 +720,7 @@ int orbfe_search_by_bow_device(int device, int npairs, int max_features, const i
     if (max_features < 1 || max_features > BOW_MAXF || row_stride > BOW_MAXF) { orbfe_set_error("at most %d features per frame", BOW_MAXF); return ORBFE_E_CAPACITY; }
     if ((uintptr_t)d_desc & 15) { orbfe_set_error("descriptor array must be 16-byte aligned"); return ORBFE_E_INVALID; }
     ORBFE_CUDA(cudaSetDevice(device));
-    k_search_by_bow<<<npairs, SB_NT, 0, (cudaStream_t)stream>>>(max_features, d_pair_kf, d_pair_f, (const uint4*)d_desc, d_kps, row_stride, d_fv_nodes, d_fv_starts,
+    k_search_by_bow<<<npairs, SBW_NT, 0, (cudaStream_t)stream>>>(max_features, d_pair_kf, d_pair_f, (const uint4*)d_desc, d_kps, row_stride, d_fv_nodes, d_fv_starts,
                                                                 d_fv_feats, d_fv_count, d_has_map_point, d_n_left, th_low, nnratio, check_orientation ? 1 : 0, kf_kf ? 1 : 0, d_match_f,
                                                                 d_kf_out, d_nmatches);
     ORBFE_CUDA(cudaGetLastError());
