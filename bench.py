@@ -1043,6 +1043,7 @@ def main():
     NP = P - 1
     d_pk, d_pf = torch.arange(0, NP, dtype=torch.int32, device="cuda"), torch.arange(1, P, dtype=torch.int32, device="cuda")
     d_sm, d_snm = torch.zeros((NP, exL.capacity), dtype=torch.int32, device="cuda"), torch.zeros(NP, dtype=torch.int32, device="cuda")
+    d_snm2 = torch.zeros(NP, dtype=torch.int32, device="cuda")
     Kc = np.array([[458.654, 0, 367.215], [0, 457.296, 248.375], [0, 0, 1]], np.float64)
     F12 = (np.linalg.inv(Kc).T @ np.array([[0, 0, 0], [0, 0, -0.11], [0, 0.11, 0]]) @ np.linalg.inv(Kc)).astype(np.float32)
     sf16 = np.array([np.float32(1.2) ** i for i in range(16)], np.float32)
@@ -1053,6 +1054,11 @@ def main():
         _lib.check(L.orbfe_search_by_bow_device(local_rank, NP, exL.capacity, d_pk.data_ptr(), d_pf.data_ptr(), vd.value, vk.value, exL.capacity, bv[5].value,
                                                 bv[6].value, bv[7].value, bv[8].value, None, None, 50, C.c_float(0.7), 1, 0, d_sm.data_ptr(), None,
                                                 d_snm.data_ptr(), st))
+
+    def sbb_self_step():     # every frame against itself: each feature finds its own row at distance 0, so nearly all of them take one
+        _lib.check(L.orbfe_search_by_bow_device(local_rank, NP, exL.capacity, d_pk.data_ptr(), d_pk.data_ptr(), vd.value, vk.value, exL.capacity, bv[5].value,
+                                                bv[6].value, bv[7].value, bv[8].value, None, None, 50, C.c_float(0.7), 1, 0, d_sm.data_ptr(), None,
+                                                d_snm2.data_ptr(), st))
 
     def sft_step():
         _lib.check(L.orbfe_search_for_triangulation_device(local_rank, NP, exL.capacity, d_pk.data_ptr(), d_pf.data_ptr(), vd.value, vk.value, None, exL.capacity,
@@ -1067,7 +1073,8 @@ def main():
     def dd_step():
         _lib.check(L.orbfe_distinctive_descriptors_device(local_rank, d_dd.data_ptr(), d_doff.data_ptr(), 20000, d_didx.data_ptr(), d_dmed.data_ptr(), st))
     consumers = {}
-    for name, fn, units, unit in (("search_by_bow", sbb_step, NP, "frame_pairs/s"), ("search_for_triangulation", sft_step, NP, "keyframe_pairs/s"),
+    for name, fn, units, unit in (("search_by_bow", sbb_step, NP, "frame_pairs/s"), ("search_by_bow_same_frame", sbb_self_step, NP, "frame_pairs/s"),
+                                  ("search_for_triangulation", sft_step, NP, "keyframe_pairs/s"),
                                   ("distinctive_descriptors", dd_step, 20000, "map_points/s")):
         for _ in range(3):
             fn()
@@ -1081,6 +1088,8 @@ def main():
         consumers[name] = {"value": units * world / (ms / 1e3), "unit": unit, "ms_per_step": ms, "per_step": units * world}
     consumers["search_by_bow"]["note"] = "ORBmatcher::SearchByBoW(pKF, F, ...) between consecutive frames of the batch, feature vectors from the transform above (device chain)"
     consumers["search_by_bow"]["matches_per_pair"] = float(d_snm.float().mean().item())
+    consumers["search_by_bow_same_frame"]["note"] = "the same call with every frame paired with itself: the load of a tracked frame, where most features take a row"
+    consumers["search_by_bow_same_frame"]["matches_per_pair"] = float(d_snm2.float().mean().item())
     consumers["search_for_triangulation"]["note"] = "ORBmatcher::SearchForTriangulation (pinhole, Pinhole::epipolarConstrain on a sideways F12) on the same pairs"
     consumers["distinctive_descriptors"]["note"] = "MapPoint::ComputeDistinctiveDescriptors, 2-15 observations per map point"
 
@@ -1150,6 +1159,43 @@ def main():
                         range(16 * cores)))
         ldt = time.perf_counter() - t0
         cpu["projection_last_frame"] = {"value": 16 * cores / ldt, "unit": "frames/s", "kind": "port", "sample": "%d frames (%.2f s wall) frame-parallel over %d threads" % (16 * cores, ldt, cores)}
+        # ---- one call at a time, as the C++ shims make them for one frame or keyframe pair: wall time of the host entry point (copies
+        #      included) beside the same inputs on one CPU thread
+        from orb_slam3_detailed_comments_kor_b200 import bow as BW
+
+        def med_ms(fn, n):
+            fn()
+            ts = []
+            for _ in range(n):
+                t0 = time.perf_counter()
+                fn()
+                ts.append(time.perf_counter() - t0)
+            return float(np.median(ts) * 1e3)
+        c0, l0, i0 = pj_cases[0], lf_cases[0], in_cases[0]
+        cpu_ex = _RO.ReferenceExtractor(*PARAMS) if reference_available() else O.OracleExtractor(*PARAMS)
+        img0 = np.ascontiguousarray(hLn[0])
+        one_call = {}
+        for name, gpu_fn, cpu_fn in (
+                ("extract", lambda: exL(img0, (0, 0)), lambda: cpu_ex(img0, (0, 0))),
+                ("search_by_projection", lambda: PJ.search_by_projection(c0["kps"], c0["desc"], c0["queries"], c0["qdesc"], c0["grid"], u_right=c0["u_right"], taken=c0["taken"]),
+                 lambda: O.search_by_projection(c0["kps"], c0["desc"], c0["queries"], c0["qdesc"], c0["grid"], u_right=c0["u_right"], taken=c0["taken"])),
+                ("search_by_projection_last_frame",
+                 lambda: PJ.search_by_projection(l0["kps"], l0["desc"], l0["queries"], l0["qdesc"], l0["grid"], u_right=l0["u_right"], taken=l0["taken"], check_orientation=True),
+                 lambda: O.search_by_projection(l0["kps"], l0["desc"], l0["queries"], l0["qdesc"], l0["grid"], u_right=l0["u_right"], taken=l0["taken"], check_orientation=True)),
+                ("search_by_bow", lambda: BW.search_by_bow(bsample[0], ksample[0], fvs[0], None, bsample[0], ksample[0], fvs[0], 50, 0.7, True),
+                 lambda: O.search_by_bow(bsample[0], ksample[0], fvs[0], None, bsample[0], ksample[0], fvs[0], 50, 0.7, True)),
+                ("search_for_triangulation",
+                 lambda: BW.search_for_triangulation(bsample[0], ksample[0], None, None, fvs[0], bsample[1], ksample[1], None, None, fvs[1], F12, [-3000.0, 240.0], scale8,
+                                                     scale8 * scale8, 50, False, False, True),
+                 lambda: O.search_for_triangulation(bsample[0], ksample[0], None, None, fvs[0], bsample[1], ksample[1], None, None, fvs[1], F12, [-3000.0, 240.0], scale8,
+                                                    scale8 * scale8, 50, False, False, True)),
+                ("search_for_initialization", lambda: PJ.search_for_initialization(*[a.copy() if hasattr(a, "copy") else a for a in i0[:6]], 100, 0.9, True),
+                 lambda: init_fn(*[a.copy() if hasattr(a, "copy") else a for a in i0[:6]], 100, 0.9, True))):
+            one_call[name] = {"gpu_host_call_ms": med_ms(gpu_fn, 20), "cpu_one_thread_ms": med_ms(cpu_fn, 3)}
+        cpu["one_call_latency"] = one_call
+        cpu["one_call_latency_note"] = ("median wall time of ONE call of the host entry point a shim makes (host arrays in, host arrays out, copies included, Python "
+                                        "ctypes glue on both sides) beside the CPU oracle / reference on one thread with the same inputs; extract = one 752x480 "
+                                        "frame; search_by_bow = a frame against itself (every feature takes a row)")
         cpu["projection"] = {"value": reps * int(pj_qoff[1]) / pdt, "unit": "map_point_searches/s",
                              "sample": "%d frames (%.2f s wall) frame-parallel over %d threads" % (reps, pdt, cores)}
 

@@ -206,7 +206,10 @@ __global__ void __launch_bounds__(BOW_NT) k_bow_assemble(const int* __restrict__
  * the stamp of an earlier unresolved query.  Queries of different nodes never share a candidate, and inside a node only queries that
  * compete for a feature both could take wait for each other. */
 #define SB_NT 256
-#define SBW_NT 1024     /* SearchByBoW: one CTA per pair, and a single pair (one Tracking call) should not wait on 8 warps */
+/* SearchByBoW: one CTA of 1024 threads per pair, so that a single pair (one Tracking call) does not wait on 8 warps; measured against 256 and
+ * 512 threads and against loading the candidates four at a time ahead of their use: this form is the fastest for one pair and within a few
+ * percent of the best for 512 pairs */
+#define SBW_NT 1024
 #define SB_FREE 0xFFFFu      /* takenBy: nobody */
 #define SB_PENDING 0x8000u   /* takenBy: taken in the running round, visible from the next one */
 struct SbSmem {
@@ -267,20 +270,12 @@ __global__ void __launch_bounds__(SBW_NT) k_search_by_bow(int maxF, const int* _
             if ((v & SB_PENDING) && v != SB_FREE) s.takenBy[i] = (uint16_t)(v & ~SB_PENDING);
         }
         __syncthreads();
-        /* the candidate loops go four rows at a time: the row numbers, then the four descriptors, are loaded before any is used, so that a
-         * thread waits for memory once per four candidates rather than twice per candidate */
 #define SB_SCAN(BODY)                                                                                                  \
-        for (int j = rg & 0xFFFF, j1 = (int)(rg >> 16); j < j1; j += 4) {                                                  \
-            int rows4[4]; uint4 da4[4], db4[4];                                                                            \
-            _Pragma("unroll") for (int k = 0; k < 4; k++) rows4[k] = featsB[min(j + k, j1 - 1)];                           \
-            _Pragma("unroll") for (int k = 0; k < 4; k++) { da4[k] = __ldg(descB + 2 * rows4[k]); db4[k] = __ldg(descB + 2 * rows4[k] + 1); } \
-            _Pragma("unroll") for (int k = 0; k < 4; k++) {                                                                \
-                if (j + k >= j1) break;                                                                                    \
-                const int row = rows4[k];                                                                                  \
-                if (SB_TAKEN_FOR(row, q)) continue;               /* if(vpMapPointMatches[realIdxF]) continue; */          \
-                const int dist = bow_ham(qa, qb, da4[k], db4[k]);                                                          \
-                BODY                                                                                                       \
-            }                                                                                                              \
+        for (int j = rg & 0xFFFF, j1 = (int)(rg >> 16); j < j1; j++) {                                                     \
+            const int row = featsB[j];                                                                                     \
+            if (SB_TAKEN_FOR(row, q)) continue;                   /* if(vpMapPointMatches[realIdxF]) continue; */          \
+            const int dist = bow_ham(qa, qb, __ldg(descB + 2 * row), __ldg(descB + 2 * row + 1));                          \
+            BODY                                                                                                           \
         }
         for (int q = tid; q < nq; q += SBW_NT) {
             if (stateB[q]) continue;

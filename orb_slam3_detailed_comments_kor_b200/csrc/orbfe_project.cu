@@ -26,7 +26,6 @@
 
 #include "orbfe_internal.h"
 
-#define PJ_NT 256
 #define PJ_MAXKP 4096
 #define PJ_COLS 64
 #define PJ_ROWS 48
@@ -41,16 +40,16 @@
 __device__ int g_pjRoundsMax, g_pjRoundsSum;   /* diagnostics: rounds of the last launches (orbfe_debug_projection_rounds) */
 
 /* Shared memory of one CTA, carved from the dynamic block by the launch's max_keypoints (the caller's promise about the frames): a
- * tracking-sized frame (1200-2000 keypoints) needs 36-44 KB and five CTAs share an SM; the full 4096 need 64 KB. */
+ * tracking-sized frame (1200-2000 keypoints) needs 36-44 KB, so that the two 512-thread CTAs an SM holds fit with room to spare; the full 4096 need 64 KB. */
 struct PjSmem {
     int* cellEnd;        /* [PJ_CELLS, twice with rigs in the batch] end of each cell's run in `sorted` (start = end of the cell before) */
     int* owner;          /* [maxKp] */
     uint32_t* taken;     /* [maxKp] low half: 1 + the first query that took the keypoint (0: occupied before the search), PJ_FREE16 = nobody;
                             high half: the same for the takes of the running round, which become visible with the next one */
     uint16_t* sorted;    /* [maxKp] */
-    int* warpSum;        /* [PJ_NT / 32] */
+    int* warpSum;        /* [32] */
 };
-static __host__ __device__ inline size_t pj_smem_bytes(int maxKp, bool rigs) { return (size_t)(rigs ? 2 : 1) * PJ_CELLS * 4 + (size_t)((maxKp + 3) & ~3) * 10 + (PJ_NT / 32) * 4; }
+static __host__ __device__ inline size_t pj_smem_bytes(int maxKp, bool rigs) { return (size_t)(rigs ? 2 : 1) * PJ_CELLS * 4 + (size_t)((maxKp + 3) & ~3) * 10 + 32 * 4; }
 /* a stereo partner row is overwritten unconditionally (src/ORBmatcher.cc:130-133), so a row can be taken more than once: what counts for a
  * query is whether ANY query before it did, i.e. the smallest taker */
 static __device__ __forceinline__ void pj_take(const PjSmem& s, int row, int q) {
@@ -128,7 +127,11 @@ static __device__ __forceinline__ void pj_window(const PjFrame& fr, const PjSmem
     }
 }
 
-__global__ void __launch_bounds__(PJ_NT) k_search_by_projection(int maxKp, const orbfe_keypoint* __restrict__ kpsAll, const uint8_t* __restrict__ descAll,
+/* NT threads per frame: 512 with two CTAs per SM for batches that fill the machine, 1024 for a call with a few frames, where one CTA's
+ * latency is the whole cost (orbfe_search_by_projection_device picks).  Loading the window's keypoints and descriptors in groups of four
+ * ahead of their use was measured too: the registers it takes cost more than the waits it saves, in both regimes. */
+template <int NT, int MINB>
+__global__ void __launch_bounds__(NT, MINB) k_search_by_projection(int maxKp, const orbfe_keypoint* __restrict__ kpsAll, const uint8_t* __restrict__ descAll,
                                                                 const int32_t* __restrict__ kpOff, const int32_t* __restrict__ nLeftAll,
                                                                 const float* __restrict__ uRightAll, const int32_t* __restrict__ partnerAll,
                                                                 const uint8_t* __restrict__ takenIn, const orbfe_frame_grid* __restrict__ grids,
@@ -165,7 +168,7 @@ __global__ void __launch_bounds__(PJ_NT) k_search_by_projection(int maxKp, const
     __shared__ int s_rot[32];
 
     if (fr.n > maxKp || fr.n > PJ_MAXKP || fr.n < 0 || nq > PJ_MAXQ) { /* the caller's promise about the frame size does not hold */
-        for (int q = tid; q < nq; q += PJ_NT) {
+        for (int q = tid; q < nq; q += NT) {
             orbfe_proj_match m;
             m.best_idx = -1; m.best_dist = 256; m.best_level = -1; m.second_dist = 256; m.second_level = -1; m.accepted = 0; m.status = ORBFE_PS_CAPACITY;
             res[q] = m;
@@ -176,10 +179,10 @@ __global__ void __launch_bounds__(PJ_NT) k_search_by_projection(int maxKp, const
     const bool stereoRig = fr.nLeft >= 0 && fr.partner != nullptr;
 
     /* ---- grid: AssignFeaturesToGrid as a counting sort ---- */
-    for (int i = tid; i < nCells; i += PJ_NT) s.cellEnd[i] = 0;
-    for (int i = tid; i < fr.n; i += PJ_NT) s.taken[i] = 0xFFFFFFFFu;
+    for (int i = tid; i < nCells; i += NT) s.cellEnd[i] = 0;
+    for (int i = tid; i < fr.n; i += NT) s.taken[i] = 0xFFFFFFFFu;
     __syncthreads();
-    for (int i = tid; i < fr.n; i += PJ_NT) {
+    for (int i = tid; i < fr.n; i += NT) {
         const float x = __ldg(&fr.kps[i].x), y = __ldg(&fr.kps[i].y);
         const int px = (int)roundf((x - fr.minx) * fr.invw), py = (int)roundf((y - fr.miny) * fr.invh);
         int c = -1;
@@ -192,7 +195,7 @@ __global__ void __launch_bounds__(PJ_NT) k_search_by_projection(int maxKp, const
     }
     __syncthreads();
     {   /* exclusive scan of the 6144 counts: 24 consecutive cells per thread */
-        const int per = nCells / PJ_NT, base = tid * per;
+        const int per = nCells / NT, base = tid * per;
         int sum = 0;
         for (int i = 0; i < per; i++) sum += s.cellEnd[base + i];
         int incl = sum;
@@ -212,12 +215,12 @@ __global__ void __launch_bounds__(PJ_NT) k_search_by_projection(int maxKp, const
         }
     }
     __syncthreads();
-    for (int i = tid; i < fr.n; i += PJ_NT) {
+    for (int i = tid; i < fr.n; i += NT) {
         const int c = s.owner[i];
         if (c >= 0) s.sorted[atomicAdd(&s.cellEnd[c], 1)] = (uint16_t)i;   /* cellEnd[c] ends up as the end of cell c */
     }
     __syncthreads();
-    for (int c = tid; c < nCells; c += PJ_NT) {   /* ascending rows inside each cell (the lists are a few entries long) */
+    for (int c = tid; c < nCells; c += NT) {   /* ascending rows inside each cell (the lists are a few entries long) */
         const int beg = c ? s.cellEnd[c - 1] : 0, end = s.cellEnd[c];
         for (int i = beg + 1; i < end; i++) {
             const uint16_t v = s.sorted[i];
@@ -226,7 +229,7 @@ __global__ void __launch_bounds__(PJ_NT) k_search_by_projection(int maxKp, const
             s.sorted[j + 1] = v;
         }
     }
-    for (int q = tid; q < nq; q += PJ_NT) {
+    for (int q = tid; q < nq; q += NT) {
         orbfe_proj_match m;
         m.best_idx = -1; m.best_dist = 256; m.best_level = -1; m.second_dist = 256; m.second_level = -1; m.accepted = 0;
         m.status = (qs[q].flags & ORBFE_PQ_SKIP) ? ORBFE_PS_SKIPPED : PJ_PENDING;
@@ -239,22 +242,22 @@ __global__ void __launch_bounds__(PJ_NT) k_search_by_projection(int maxKp, const
      * every round while it waits.  So only the earliest PJ_FRONT unresolved queries take part: the rule of step B needs the stamps
      * of all EARLIER unresolved queries, and those are inside the front by construction. */
     __shared__ int s_front;
-    int myFirst = tid;   /* my first query that may still be unresolved (I own tid, tid + PJ_NT, ...) */
+    int myFirst = tid;   /* my first query that may still be unresolved (I own tid, tid + NT, ...) */
     int rounds = 0;
     for (;;) {
-        for (int i = tid; i < fr.n; i += PJ_NT) {
+        for (int i = tid; i < fr.n; i += NT) {
             s.owner[i] = INT_MAX;
             const uint32_t w = s.taken[i];
             if ((w >> 16) != PJ_FREE16) s.taken[i] = 0xFFFF0000u | min(w & 0xFFFFu, w >> 16);
         }
         if (tid == 0) s_front = INT_MAX;
         __syncthreads();
-        while (myFirst < nq && status[myFirst * 7] != PJ_PENDING) myFirst += PJ_NT;
+        while (myFirst < nq && status[myFirst * 7] != PJ_PENDING) myFirst += NT;
         if (myFirst < nq) atomicMin(&s_front, myFirst);
         __syncthreads();
         const int limit = s_front > INT_MAX - PJ_FRONT ? INT_MAX : s_front + PJ_FRONT;
         /* A. stamps */
-        for (int q = myFirst; q < nq && q < limit; q += PJ_NT) {
+        for (int q = myFirst; q < nq && q < limit; q += NT) {
             if (status[q * 7] != PJ_PENDING) continue;
             const orbfe_proj_query p = qs[q];
             if (p.flags & (ORBFE_PQ_AFTER_LEFT | ORBFE_PQ_NEEDS_LEFT_WINDOW))
@@ -277,7 +280,7 @@ __global__ void __launch_bounds__(PJ_NT) k_search_by_projection(int maxKp, const
         __syncthreads();
         /* B. scan, decide */
         int pending = 0;
-        for (int q = myFirst; q < nq; q += PJ_NT) {
+        for (int q = myFirst; q < nq; q += NT) {
             if (q >= limit) { pending++; break; }   /* behind the front: waits */
             if (status[q * 7] != PJ_PENDING) continue;
             const orbfe_proj_query p = qs[q];
@@ -293,6 +296,7 @@ __global__ void __launch_bounds__(PJ_NT) k_search_by_projection(int maxKp, const
             }
             const uint4 qa = __ldg(qdesc + 2 * q), qb = __ldg(qdesc + 2 * q + 1);
             int bestDist = 256, bestLevel = -1, bestDist2 = 256, bestLevel2 = -1, bestIdx = -1, seen = 0;
+            int foreign = 257;   /* the closest candidate that carries the stamp of an earlier unresolved query */
             pj_window(fr, s, p, [&](int row, int oct) {
                 seen++;
                 if (PJ_TAKEN_FOR(s, row, q)) return;
@@ -300,6 +304,7 @@ __global__ void __launch_bounds__(PJ_NT) k_search_by_projection(int maxKp, const
                 const int dist = pj_ham(qa, qb, __ldg(fr.desc + 2 * row), __ldg(fr.desc + 2 * row + 1));
                 if (dist < bestDist) { bestDist2 = bestDist; bestDist = dist; bestLevel2 = bestLevel; bestLevel = oct; bestIdx = row; }
                 else if (dist < bestDist2) { bestLevel2 = oct; bestDist2 = dist; }
+                if (s.owner[row] < q) foreign = min(foreign, dist);
             });
             int st = seen ? ORBFE_PS_NO_CANDIDATES : ORBFE_PS_EMPTY_WINDOW;
             bool blocked = false;
@@ -308,12 +313,7 @@ __global__ void __launch_bounds__(PJ_NT) k_search_by_projection(int maxKp, const
                 const bool bestOnly = (p.flags & ORBFE_PQ_BEST_ONLY) != 0;
                 st = bestDist > thHigh ? ORBFE_PS_OVER_THRESHOLD
                      : (!bestOnly && bestLevel == bestLevel2 && (float)bestDist > nnratio * (float)bestDist2) ? ORBFE_PS_RATIO_REJECTED : ORBFE_PS_ACCEPTED;
-                const int reach = bestDist2;   /* candidates above it cannot change any reported field */
-                pj_window(fr, s, p, [&](int row, int oct) {
-                    if (blocked || PJ_TAKEN_FOR(s, row, q)) return;
-                    if (pj_gated(fr, p, row, oct, gateRight)) return;
-                    if (s.owner[row] < q && pj_ham(qa, qb, __ldg(fr.desc + 2 * row), __ldg(fr.desc + 2 * row + 1)) <= reach) blocked = true;
-                });
+                blocked = foreign <= bestDist2;   /* candidates above the second best cannot change any reported field */
                 if (st == ORBFE_PS_ACCEPTED && stereoRig) {
                     const int pt = __ldg(fr.partner + bestIdx);
                     if (pt >= 0 && pt < fr.n) { partnerRow = pt; if (s.owner[pt] < q) blocked = true; }
@@ -338,7 +338,7 @@ __global__ void __launch_bounds__(PJ_NT) k_search_by_projection(int maxKp, const
         const float factor = 1.0f / 30.0f;   /* 1.0f/HISTO_LENGTH */
         if (tid < 32) s_rot[tid] = 0;
         __syncthreads();
-        for (int q = tid; q < nq; q += PJ_NT) {
+        for (int q = tid; q < nq; q += NT) {
             if (status[q * 7] != ORBFE_PS_ACCEPTED) continue;
             float rot = qs[q].angle - __ldg(&fr.kps[res[q].best_idx].angle);
             if (rot < 0.0f) rot += 360.0f;
@@ -361,7 +361,7 @@ __global__ void __launch_bounds__(PJ_NT) k_search_by_projection(int maxKp, const
         }
         __syncthreads();
         const int ind1 = s_rot[30], ind2 = (int)(signed char)(s_rot[31] & 0xFF), ind3 = (int)(signed char)((s_rot[31] >> 8) & 0xFF);
-        for (int q = tid; q < nq; q += PJ_NT) {
+        for (int q = tid; q < nq; q += NT) {
             if (status[q * 7] != ORBFE_PS_ACCEPTED) continue;
             const int row = res[q].best_idx;
             float rot = qs[q].angle - __ldg(&fr.kps[row].angle);
@@ -377,7 +377,7 @@ __global__ void __launch_bounds__(PJ_NT) k_search_by_projection(int maxKp, const
         __syncthreads();
     }
     if (takenOut)
-        for (int i = tid; i < fr.n; i += PJ_NT) takenOut[k0 + i] = s.taken[i] != 0xFFFFFFFFu ? 1 : 0;
+        for (int i = tid; i < fr.n; i += NT) takenOut[k0 + i] = s.taken[i] != 0xFFFFFFFFu ? 1 : 0;
 }
 
 extern "C" {
@@ -404,14 +404,22 @@ int orbfe_search_by_projection_device(int device, int nframes, int max_keypoints
     if (max_keypoints < 0 || max_keypoints > PJ_MAXKP) { orbfe_set_error("at most %d keypoints per frame (both cameras together)", PJ_MAXKP); return ORBFE_E_CAPACITY; }
     if (((uintptr_t)d_desc | (uintptr_t)d_qdesc) & 15) { orbfe_set_error("descriptor arrays must be 16-byte aligned"); return ORBFE_E_INVALID; }
     ORBFE_CUDA(cudaSetDevice(device));
+    typedef void (*PjKernel)(int, const orbfe_keypoint*, const uint8_t*, const int32_t*, const int32_t*, const float*, const int32_t*, const uint8_t*,
+                             const orbfe_frame_grid*, const orbfe_proj_query*, const uint8_t*, const int32_t*, int, float, int, const float*, orbfe_proj_match*, uint8_t*);
+    int sms = 0;
+    ORBFE_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+    const bool few = nframes <= 2 * sms;                      /* not enough frames to fill the SMs with 512-thread CTAs */
+    const PjKernel fn = few ? (PjKernel)k_search_by_projection<1024, 1> : (PjKernel)k_search_by_projection<512, 2>;
+    const int nt = few ? 1024 : 512;
     static thread_local int configured = -1;
     if (configured != device) {
-        ORBFE_CUDA(cudaFuncSetAttribute(k_search_by_projection, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pj_smem_bytes(PJ_MAXKP, true)));
+        ORBFE_CUDA(cudaFuncSetAttribute(k_search_by_projection<1024, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pj_smem_bytes(PJ_MAXKP, true)));
+        ORBFE_CUDA(cudaFuncSetAttribute(k_search_by_projection<512, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pj_smem_bytes(PJ_MAXKP, true)));
         configured = device;
     }
-    k_search_by_projection<<<nframes, PJ_NT, pj_smem_bytes(max_keypoints, d_n_left != nullptr), (cudaStream_t)stream>>>(max_keypoints, d_kps, d_desc, d_kp_offsets, d_n_left, d_u_right, d_partner,
-                                                                                    d_taken_in, d_grids, d_queries, d_qdesc, d_q_offsets, th_high, nnratio,
-                                                                                    check_orientation ? 1 : 0, d_inv_level_sigma2, d_out, d_taken_out);
+    fn<<<nframes, nt, pj_smem_bytes(max_keypoints, d_n_left != nullptr), (cudaStream_t)stream>>>(max_keypoints, d_kps, d_desc, d_kp_offsets, d_n_left, d_u_right, d_partner,
+                                                                                 d_taken_in, d_grids, d_queries, d_qdesc, d_q_offsets, th_high, nnratio,
+                                                                                 check_orientation ? 1 : 0, d_inv_level_sigma2, d_out, d_taken_out);
     ORBFE_CUDA(cudaGetLastError());
     return ORBFE_OK;
 }

@@ -31,4 +31,12 @@ for name, kw in [("bench", dict(n=1200, nq=1500, th=1.0, stereo_gate=True)), ("t
     for _ in range(10): step()
     e1.record(); torch.cuda.synchronize()
     L.orbfe_debug_projection_rounds(C.byref(a), C.byref(b))
-    print("%-10s %.3f ms per %d frames; rounds max %d mean %.1f" % (name, e0.elapsed_time(e1) / 10, PF, a.value, b.value / (10 * PF)), flush=True)
+    c0 = cases[0]
+    def one():
+        PJ.search_by_projection(c0["kps"], c0["desc"], c0["queries"], c0["qdesc"], c0["grid"], u_right=c0.get("u_right"), taken=c0["taken"],
+                                check_orientation=bool(c0["check_orientation"][0]))
+    import time
+    one(); ts = []
+    for _ in range(20):
+        t0 = time.perf_counter(); one(); ts.append(time.perf_counter() - t0)
+    print("%-10s %.3f ms per %d frames; rounds max %d mean %.1f; one host call %.3f ms" % (name, e0.elapsed_time(e1) / 10, PF, a.value, b.value / (10 * PF), np.median(ts) * 1e3), flush=True)

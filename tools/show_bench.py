@@ -21,3 +21,5 @@ for l in sys.stdin:
     print("initialization", d.get("initialization"), "| serial step ms", (d.get("config") or {}).get("serial_ms_per_step"))
     print("consumers", d.get("consumers"))
     print("cpu consumers", {k: (d.get("cpu_baseline") or {}).get(k) for k in ("search_by_bow", "search_for_triangulation", "distinctive_descriptors", "initialization")})
+    for k, v in ((d.get("cpu_baseline") or {}).get("one_call_latency") or {}).items():
+        print("one call %-34s gpu host call %.3f ms | cpu one thread %.3f ms" % (k, v["gpu_host_call_ms"], v["cpu_one_thread_ms"]))
