@@ -48,8 +48,17 @@ struct PjSmem {
                             high half: the same for the takes of the running round, which become visible with the next one */
     uint16_t* sorted;    /* [maxKp] */
     int* warpSum;        /* [32] */
+    /* CACHE: what a window walk reads of a keypoint, in the order of `sorted` (a window column is one contiguous run), so that the walks —
+     * three per query and round, every step a dependent load — go to shared memory instead of L2 */
+    uint4* descS;        /* [2 * maxKp] */
+    float2* xyS;         /* [maxKp] */
+    int* octS;           /* [maxKp] */
+    float* urS;          /* [maxKp] mvuRight, -1 without one */
 };
-static __host__ __device__ inline size_t pj_smem_bytes(int maxKp, bool rigs) { return (size_t)(rigs ? 2 : 1) * PJ_CELLS * 4 + (size_t)((maxKp + 3) & ~3) * 10 + 32 * 4; }
+#define PJ_CACHE_BYTES_PER_KP 48
+static __host__ __device__ inline size_t pj_smem_bytes(int maxKp, bool rigs, bool cache) {
+    return (size_t)(rigs ? 2 : 1) * PJ_CELLS * 4 + (size_t)((maxKp + 3) & ~3) * (10 + (cache ? PJ_CACHE_BYTES_PER_KP : 0)) + 32 * 4;
+}
 /* a stereo partner row is overwritten unconditionally (src/ORBmatcher.cc:130-133), so a row can be taken more than once: what counts for a
  * query is whether ANY query before it did, i.e. the smallest taker */
 static __device__ __forceinline__ void pj_take(const PjSmem& s, int row, int q) {
@@ -74,11 +83,13 @@ struct PjFrame {
 
 /* the per-candidate gate on mvuRight: |xr - mvuRight| <= radius for the SearchByProjection overloads (rectified rigs only), the
  * chi-square reprojection test of ORBmatcher::Fuse for ORBFE_PQ_ERROR_GATE queries.  true = the candidate is skipped. */
-static __device__ __forceinline__ bool pj_gated(const PjFrame& fr, const orbfe_proj_query& p, int row, int oct, bool gateRight) {
+template <bool CACHE>
+static __device__ __forceinline__ bool pj_gated(const PjFrame& fr, const PjSmem& s, const orbfe_proj_query& p, int row, int j, int oct, bool gateRight) {
     if ((p.flags & ORBFE_PQ_ERROR_GATE) && fr.invSigma2) {
-        const float ex = __fsub_rn(p.x, __ldg(&fr.kps[row].x)), ey = __fsub_rn(p.y, __ldg(&fr.kps[row].y));
+        const float kx = CACHE ? s.xyS[j].x : __ldg(&fr.kps[row].x), ky = CACHE ? s.xyS[j].y : __ldg(&fr.kps[row].y);
+        const float ex = __fsub_rn(p.x, kx), ey = __fsub_rn(p.y, ky);
         const float is2 = __ldg(fr.invSigma2 + oct);
-        const float ur = fr.uRight ? __ldg(fr.uRight + row) : -1.0f;
+        const float ur = CACHE ? s.urS[j] : (fr.uRight ? __ldg(fr.uRight + row) : -1.0f);
         if (ur >= 0) {
             const float er = __fsub_rn(p.xr, ur);
             const float e2 = __fadd_rn(__fadd_rn(__fmul_rn(ex, ex), __fmul_rn(ey, ey)), __fmul_rn(er, er));
@@ -88,7 +99,7 @@ static __device__ __forceinline__ bool pj_gated(const PjFrame& fr, const orbfe_p
         return (double)__fmul_rn(e2, is2) > 5.99;
     }
     if (gateRight) {
-        const float ur = __ldg(fr.uRight + row);
+        const float ur = CACHE ? s.urS[j] : __ldg(fr.uRight + row);
         if (ur > 0 && fabsf(p.xr - ur) > p.radius) return true;
     }
     return false;
@@ -100,7 +111,7 @@ static __device__ __forceinline__ int pj_ham(const uint4 qa, const uint4 qb, con
 }
 
 /* Frame::GetFeaturesInArea: visit(row, octave) for every keypoint of the window, in the reference's order */
-template <class F>
+template <bool CACHE, class F>
 static __device__ __forceinline__ void pj_window(const PjFrame& fr, const PjSmem& s, const orbfe_proj_query& p, F&& visit) {
     const float r = p.radius, ax = p.x - fr.minx, ay = p.y - fr.miny;
     const int x0 = max(0, (int)floorf((ax - r) * fr.invw));
@@ -119,10 +130,17 @@ static __device__ __forceinline__ void pj_window(const PjFrame& fr, const PjSmem
         const int beg = c0 ? s.cellEnd[c0 - 1] : 0, end = s.cellEnd[c1];
         for (int j = beg; j < end; j++) {
             const int row = s.sorted[j];
-            const orbfe_keypoint* kp = fr.kps + row;
-            const int oct = __ldg(&kp->octave);
-            if (oct < p.min_level || (p.max_level >= 0 && oct > p.max_level)) continue;
-            if (fabsf(__ldg(&kp->x) - p.x) < r && fabsf(__ldg(&kp->y) - p.y) < r) visit(row, oct);
+            if (CACHE) {
+                const int oct = s.octS[j];
+                if (oct < p.min_level || (p.max_level >= 0 && oct > p.max_level)) continue;
+                const float2 xy = s.xyS[j];
+                if (fabsf(xy.x - p.x) < r && fabsf(xy.y - p.y) < r) visit(row, oct, j);
+            } else {
+                const orbfe_keypoint* kp = fr.kps + row;
+                const int oct = __ldg(&kp->octave);
+                if (oct < p.min_level || (p.max_level >= 0 && oct > p.max_level)) continue;
+                if (fabsf(__ldg(&kp->x) - p.x) < r && fabsf(__ldg(&kp->y) - p.y) < r) visit(row, oct, j);
+            }
         }
     }
 }
@@ -130,7 +148,7 @@ static __device__ __forceinline__ void pj_window(const PjFrame& fr, const PjSmem
 /* NT threads per frame: 512 with two CTAs per SM for batches that fill the machine, 1024 for a call with a few frames, where one CTA's
  * latency is the whole cost (orbfe_search_by_projection_device picks).  Loading the window's keypoints and descriptors in groups of four
  * ahead of their use was measured too: the registers it takes cost more than the waits it saves, in both regimes. */
-template <int NT, int MINB>
+template <int NT, int MINB, bool CACHE>
 __global__ void __launch_bounds__(NT, MINB) k_search_by_projection(int maxKp, const orbfe_keypoint* __restrict__ kpsAll, const uint8_t* __restrict__ descAll,
                                                                 const int32_t* __restrict__ kpOff, const int32_t* __restrict__ nLeftAll,
                                                                 const float* __restrict__ uRightAll, const int32_t* __restrict__ partnerAll,
@@ -143,7 +161,13 @@ __global__ void __launch_bounds__(NT, MINB) k_search_by_projection(int maxKp, co
     PjSmem s;
     {
         const int cap = (maxKp + 3) & ~3;
-        s.cellEnd = reinterpret_cast<int*>(pj_raw);
+        unsigned char* base = pj_raw;
+        s.descS = reinterpret_cast<uint4*>(base);
+        s.xyS = reinterpret_cast<float2*>(base + (CACHE ? (size_t)cap * 32 : 0));
+        s.octS = reinterpret_cast<int*>(base + (CACHE ? (size_t)cap * 40 : 0));
+        s.urS = reinterpret_cast<float*>(base + (CACHE ? (size_t)cap * 44 : 0));
+        if (CACHE) base += (size_t)cap * PJ_CACHE_BYTES_PER_KP;
+        s.cellEnd = reinterpret_cast<int*>(base);
         s.owner = s.cellEnd + nCells;
         s.taken = reinterpret_cast<uint32_t*>(s.owner + cap);
         s.sorted = reinterpret_cast<uint16_t*>(s.taken + cap);
@@ -236,6 +260,21 @@ __global__ void __launch_bounds__(NT, MINB) k_search_by_projection(int maxKp, co
         res[q] = m;
     }
     __syncthreads();
+    if (CACHE) {
+        const int ns = s.cellEnd[nCells - 1];
+        for (int j = tid; j < ns; j += NT) {
+            const int row = s.sorted[j];
+            const orbfe_keypoint* kp = fr.kps + row;
+            s.xyS[j] = make_float2(__ldg(&kp->x), __ldg(&kp->y));
+            s.octS[j] = __ldg(&kp->octave);
+            s.urS[j] = fr.uRight ? __ldg(fr.uRight + row) : -1.0f;
+            s.descS[2 * j] = __ldg(fr.desc + 2 * row);
+            s.descS[2 * j + 1] = __ldg(fr.desc + 2 * row + 1);
+        }
+        __syncthreads();
+    }
+#define PJ_DESC_A(row, j) (CACHE ? s.descS[2 * (j)] : __ldg(fr.desc + 2 * (row)))
+#define PJ_DESC_B(row, j) (CACHE ? s.descS[2 * (j) + 1] : __ldg(fr.desc + 2 * (row) + 1))
 
     /* ---- rounds ----
      * A round costs (participants x window); a query behind a long chain of earlier ones over the same keypoints would pay that
@@ -266,10 +305,10 @@ __global__ void __launch_bounds__(NT, MINB) k_search_by_projection(int maxKp, co
             /* what a query takes is its best candidate, and that has to be within thHigh: only those rows (and their partners) get its
              * stamp.  With stamps on the whole window, queries whose windows overlap resolved one per round whether or not they competed. */
             const uint4 sa = __ldg(qdesc + 2 * q), sb = __ldg(qdesc + 2 * q + 1);
-            pj_window(fr, s, p, [&](int row, int oct) {
+            pj_window<CACHE>(fr, s, p, [&](int row, int oct, int j) {
                 if (PJ_TAKEN_FOR(s, row, q)) return;
-                if (pj_gated(fr, p, row, oct, gateRight)) return;
-                if (pj_ham(sa, sb, __ldg(fr.desc + 2 * row), __ldg(fr.desc + 2 * row + 1)) > thHigh) return;
+                if (pj_gated<CACHE>(fr, s, p, row, j, oct, gateRight)) return;
+                if (pj_ham(sa, sb, PJ_DESC_A(row, j), PJ_DESC_B(row, j)) > thHigh) return;
                 atomicMin(&s.owner[row], q);
                 if (stereoRig) {
                     const int pt = __ldg(fr.partner + row);
@@ -297,11 +336,11 @@ __global__ void __launch_bounds__(NT, MINB) k_search_by_projection(int maxKp, co
             const uint4 qa = __ldg(qdesc + 2 * q), qb = __ldg(qdesc + 2 * q + 1);
             int bestDist = 256, bestLevel = -1, bestDist2 = 256, bestLevel2 = -1, bestIdx = -1, seen = 0;
             int foreign = 257;   /* the closest candidate that carries the stamp of an earlier unresolved query */
-            pj_window(fr, s, p, [&](int row, int oct) {
+            pj_window<CACHE>(fr, s, p, [&](int row, int oct, int j) {
                 seen++;
                 if (PJ_TAKEN_FOR(s, row, q)) return;
-                if (pj_gated(fr, p, row, oct, gateRight)) return;
-                const int dist = pj_ham(qa, qb, __ldg(fr.desc + 2 * row), __ldg(fr.desc + 2 * row + 1));
+                if (pj_gated<CACHE>(fr, s, p, row, j, oct, gateRight)) return;
+                const int dist = pj_ham(qa, qb, PJ_DESC_A(row, j), PJ_DESC_B(row, j));
                 if (dist < bestDist) { bestDist2 = bestDist; bestDist = dist; bestLevel2 = bestLevel; bestLevel = oct; bestIdx = row; }
                 else if (dist < bestDist2) { bestLevel2 = oct; bestDist2 = dist; }
                 if (s.owner[row] < q) foreign = min(foreign, dist);
@@ -406,20 +445,28 @@ int orbfe_search_by_projection_device(int device, int nframes, int max_keypoints
     ORBFE_CUDA(cudaSetDevice(device));
     typedef void (*PjKernel)(int, const orbfe_keypoint*, const uint8_t*, const int32_t*, const int32_t*, const float*, const int32_t*, const uint8_t*,
                              const orbfe_frame_grid*, const orbfe_proj_query*, const uint8_t*, const int32_t*, int, float, int, const float*, orbfe_proj_match*, uint8_t*);
-    int sms = 0;
+    int sms = 0, smemMax = 0;
     ORBFE_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+    ORBFE_CUDA(cudaDeviceGetAttribute(&smemMax, cudaDevAttrMaxSharedMemoryPerBlockOptin, device));
+    smemMax -= 1024;                                           /* the kernel's few static words, and slack */
     const bool few = nframes <= 2 * sms;                      /* not enough frames to fill the SMs with 512-thread CTAs */
-    const PjKernel fn = few ? (PjKernel)k_search_by_projection<1024, 1> : (PjKernel)k_search_by_projection<512, 2>;
+    const bool rigs = d_n_left != nullptr;
+    /* the keypoints' window data in shared memory when it fits: for a batch twice per SM beside each other, for a few frames once */
+    const bool cache = pj_smem_bytes(max_keypoints, rigs, true) <= (size_t)(few ? smemMax : smemMax / 2 - 1024);
+    const PjKernel fn = few ? (cache ? (PjKernel)k_search_by_projection<1024, 1, true> : (PjKernel)k_search_by_projection<1024, 1, false>)
+                            : (cache ? (PjKernel)k_search_by_projection<512, 2, true> : (PjKernel)k_search_by_projection<512, 2, false>);
     const int nt = few ? 1024 : 512;
     static thread_local int configured = -1;
     if (configured != device) {
-        ORBFE_CUDA(cudaFuncSetAttribute(k_search_by_projection<1024, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pj_smem_bytes(PJ_MAXKP, true)));
-        ORBFE_CUDA(cudaFuncSetAttribute(k_search_by_projection<512, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pj_smem_bytes(PJ_MAXKP, true)));
+        ORBFE_CUDA(cudaFuncSetAttribute(k_search_by_projection<1024, 1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smemMax));
+        ORBFE_CUDA(cudaFuncSetAttribute(k_search_by_projection<512, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smemMax));
+        ORBFE_CUDA(cudaFuncSetAttribute(k_search_by_projection<1024, 1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pj_smem_bytes(PJ_MAXKP, true, false)));
+        ORBFE_CUDA(cudaFuncSetAttribute(k_search_by_projection<512, 2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pj_smem_bytes(PJ_MAXKP, true, false)));
         configured = device;
     }
-    fn<<<nframes, nt, pj_smem_bytes(max_keypoints, d_n_left != nullptr), (cudaStream_t)stream>>>(max_keypoints, d_kps, d_desc, d_kp_offsets, d_n_left, d_u_right, d_partner,
-                                                                                 d_taken_in, d_grids, d_queries, d_qdesc, d_q_offsets, th_high, nnratio,
-                                                                                 check_orientation ? 1 : 0, d_inv_level_sigma2, d_out, d_taken_out);
+    fn<<<nframes, nt, pj_smem_bytes(max_keypoints, rigs, cache), (cudaStream_t)stream>>>(max_keypoints, d_kps, d_desc, d_kp_offsets, d_n_left, d_u_right, d_partner,
+                                                                         d_taken_in, d_grids, d_queries, d_qdesc, d_q_offsets, th_high, nnratio,
+                                                                         check_orientation ? 1 : 0, d_inv_level_sigma2, d_out, d_taken_out);
     ORBFE_CUDA(cudaGetLastError());
     return ORBFE_OK;
 }
@@ -463,7 +510,7 @@ int orbfe_search_by_projection(int device, const orbfe_keypoint* kps, const uint
     if (inv_level_sigma2) memcpy(h + oSig, inv_level_sigma2, 16 * sizeof(float));
     cudaError_t e = cudaMemcpyAsync(d, h, inEnd, cudaMemcpyHostToDevice, ws.stream);
     if (e == cudaSuccess)
-        rc = orbfe_search_by_projection_device(device, 1, PJ_MAXKP, (const orbfe_keypoint*)(d + oKps), d + oDesc, (const int32_t*)(d + oOff),
+        rc = orbfe_search_by_projection_device(device, 1, n > 0 ? n : 1, (const orbfe_keypoint*)(d + oKps), d + oDesc, (const int32_t*)(d + oOff),
                                                (const int32_t*)(d + oOff) + 4, u_right ? (const float*)(d + oUr) : nullptr,
                                                partner ? (const int32_t*)(d + oPt) : nullptr, taken ? d + oTk : nullptr, (const orbfe_frame_grid*)(d + oGrid),
                                                (const orbfe_proj_query*)(d + oQ), d + oQd, (const int32_t*)(d + oOff) + 2, th_high, nnratio, check_orientation,

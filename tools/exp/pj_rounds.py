@@ -31,6 +31,19 @@ for name, kw in [("bench", dict(n=1200, nq=1500, th=1.0, stereo_gate=True)), ("t
     for _ in range(10): step()
     e1.record(); torch.cuda.synchronize()
     L.orbfe_debug_projection_rounds(C.byref(a), C.byref(b))
+    def step1():
+        PJ.search_by_projection_device(1, MAXKP, d["kps"].data_ptr(), d["desc"].data_ptr(), d["koff"].data_ptr(), d["grid"].data_ptr(), d["queries"].data_ptr(),
+                                       d["qdesc"].data_ptr(), d["qoff"].data_ptr(), out.data_ptr(), d_u_right=ur.data_ptr() if ur is not None else None,
+                                       d_taken_in=d["taken"].data_ptr(), check_orientation=bool(cases[0]["check_orientation"][0]))
+    for _ in range(3): step1()
+    torch.cuda.synchronize()
+    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    f0.record()
+    for _ in range(20): step1()
+    f1.record(); torch.cuda.synchronize()
+    one_kernel = f0.elapsed_time(f1) / 20
+    L.orbfe_debug_projection_rounds(C.byref(a), C.byref(b))
+    print("   one frame on the device: %.3f ms (20 launches back to back), rounds %d" % (one_kernel, a.value))
     c0 = cases[0]
     def one():
         PJ.search_by_projection(c0["kps"], c0["desc"], c0["queries"], c0["qdesc"], c0["grid"], u_right=c0.get("u_right"), taken=c0["taken"],
