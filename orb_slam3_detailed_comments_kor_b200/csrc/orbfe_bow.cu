@@ -208,10 +208,11 @@ __global__ void __launch_bounds__(BOW_NT) k_bow_assemble(const int* __restrict__
 #define SB_NT 256
 /* SearchByBoW: one CTA of 1024 threads per pair, so that a single pair (one Tracking call) does not wait on 8 warps; measured against 256 and
  * 512 threads and against loading the candidates four at a time ahead of their use: this form is the fastest for one pair and within a few
- * percent of the best for 512 pairs */
+ * percent of the best for 512 pairs.  The frame's descriptors in shared memory (in feature-vector order) changed nothing measurable. */
 #define SBW_NT 1024
 #define SB_FREE 0xFFFFu      /* takenBy: nobody */
 #define SB_PENDING 0x8000u   /* takenBy: taken in the running round, visible from the next one */
+__device__ int g_sbRoundsMax, g_sbRoundsSum;   /* diagnostics: rounds of the last launches (orbfe_debug_bow_rounds) */
 struct SbSmem {
     int owner[BOW_MAXF];
     uint32_t range[BOW_MAXF];          /* per query: first | last+1 << 16 of its node's run in the frame's fvFeats (0 = none) */
@@ -263,6 +264,7 @@ __global__ void __launch_bounds__(SBW_NT) k_search_by_bow(int maxF, const int* _
      * it takes is its best one, and that must pass the threshold): only those get its stamp.  With stamps on the node's whole run the
      * queries of a node would resolve one per round even when nothing matches. */
 #define SB_TAKEN_FOR(row, q) ((unsigned)s.takenBy[row] <= (unsigned)(q))   /* stored q' + 1 <= q  <=>  q' < q; pending and free values are >= 0x8000 */
+    int rounds = 0;
     for (;;) {
         for (int i = tid; i < maxF; i += SBW_NT) {
             s.owner[i] = INT_MAX;
@@ -314,8 +316,10 @@ __global__ void __launch_bounds__(SBW_NT) k_search_by_bow(int maxF, const int* _
             if (ok) { mF[bestIdx] = rowA; s.takenBy[bestIdx] = (uint16_t)((q + 1) | SB_PENDING); }
             if (okR) { mF[bestIdxR] = rowA; s.takenBy[bestIdxR] = (uint16_t)((q + 1) | SB_PENDING); }
         }
+        rounds++;
         if (__syncthreads_count(pending) == 0) break;
     }
+    if (tid == 0) { atomicMax(&g_sbRoundsMax, rounds); atomicAdd(&g_sbRoundsSum, rounds); }
 #undef SB_SCAN
 #undef SB_TAKEN_FOR
     /* rotation consistency (:368-384, 440-458) */
@@ -703,6 +707,19 @@ int orbfe_bow_device_views(orbfe_vocabulary* v, const int32_t** d_feat_word, con
     if (d_fv_starts) *d_fv_starts = v->fvStarts;
     if (d_fv_feats) *d_fv_feats = v->fvFeats;
     if (d_fv_count) *d_fv_count = v->fvCount;
+    return ORBFE_OK;
+}
+
+/* diagnostics: maximum and sum over the CTAs (pairs) of the rounds k_search_by_bow needed since the last call; resets both */
+int orbfe_debug_bow_rounds(int* max_rounds, int* sum_rounds) {
+    int z = 0, a = 0, b = 0;
+    ORBFE_CUDA(cudaDeviceSynchronize());
+    ORBFE_CUDA(cudaMemcpyFromSymbol(&a, g_sbRoundsMax, sizeof a));
+    ORBFE_CUDA(cudaMemcpyFromSymbol(&b, g_sbRoundsSum, sizeof b));
+    ORBFE_CUDA(cudaMemcpyToSymbol(g_sbRoundsMax, &z, sizeof z));
+    ORBFE_CUDA(cudaMemcpyToSymbol(g_sbRoundsSum, &z, sizeof z));
+    if (max_rounds) *max_rounds = a;
+    if (sum_rounds) *sum_rounds = b;
     return ORBFE_OK;
 }
 

@@ -149,3 +149,58 @@ def test_gpu_search_batch_device():
         want, wtaken, _ = _run(O.search_by_projection, c)
         assert np.array_equal(_as_matrix(got), _as_matrix(want)), "frame %d" % i
         assert np.array_equal(tko[koff[i]:koff[i + 1]], wtaken), "frame %d occupancy" % i
+
+
+@pytest.mark.gpu
+def test_gpu_host_entry_points_from_several_threads_and_release():
+    """The one-frame host entry points stage their arguments through a block that belongs to the calling thread.  Four threads call at the
+    same time with sizes that change from call to call (the block grows and is reused), give the block back in between
+    (orbfe_thread_release) and call again; every result must equal the oracle's.  A large batch of frames (more than two per SM: the
+    512-thread kernel without the shared-memory cache at 4096 keypoints) and a small one go through the device entry point too."""
+    from concurrent.futures import ThreadPoolExecutor
+    from orb_slam3_detailed_comments_kor_b200 import projection as P
+    from orb_slam3_detailed_comments_kor_b200 import _lib
+    cases = [PC.make_case(seed=60 + i, n=n, nq=nq, th=th, crowd=crowd, stereo_gate=True, last_frame=lf)
+             for i, (n, nq, th, crowd, lf) in enumerate([(300, 200, 1.0, 0.0, None), (2500, 3000, 3.0, 0.3, None), (40, 900, 15.0, 1.0, "still"),
+                                                         (4096, 5000, 1.0, 0.0, None), (1200, 1200, 7.0, 0.2, "forward"), (1, 3, 1.0, 0.0, None)])]
+    wants = [_run(O.search_by_projection, c) for c in cases]
+
+    def worker(t):
+        bad = []
+        for rep in range(3):
+            for k in range(len(cases)):
+                i = (k + t) % len(cases)
+                out, taken, nm = _run(P.search_by_projection, cases[i])
+                if not (np.array_equal(_as_matrix(out), _as_matrix(wants[i][0])) and np.array_equal(taken, wants[i][1]) and nm == wants[i][2]):
+                    bad.append((t, rep, i))
+            _lib.lib().orbfe_thread_release()
+        return bad
+    with ThreadPoolExecutor(4) as tp:
+        res = list(tp.map(worker, range(4)))
+    assert not any(res), res
+    _lib.lib().orbfe_thread_release()     # a thread that holds nothing: no-op
+    out, taken, nm = _run(P.search_by_projection, cases[0])
+    assert np.array_equal(_as_matrix(out), _as_matrix(wants[0][0])) and nm == wants[0][2]
+    # more than two frames per SM: the 512-thread kernel, without the shared-memory cache (4096 keypoints promised) and with it (1300)
+    import torch
+    for sel, maxkp in (([0, 1, 2, 3, 4, 5], 4096), ([0, 2, 4, 5], 1300)):
+        order = [sel[i % len(sel)] for i in range(330)]
+        cat = lambda k: np.concatenate([cases[i][k] for i in order])  # noqa: E731
+        koff = np.cumsum([0] + [len(cases[i]["kps"]) for i in order]).astype(np.int32)
+        qoff = np.cumsum([0] + [len(cases[i]["queries"]) for i in order]).astype(np.int32)
+        dev = lambda a: torch.from_numpy(np.ascontiguousarray(a).view(np.uint8).reshape(-1)).cuda()  # noqa: E731
+        d_kps, d_desc, d_q, d_qd = dev(cat("kps")), dev(cat("desc")), dev(cat("queries")), dev(cat("qdesc"))
+        d_ur, d_tk, d_grid = dev(cat("u_right")), dev(cat("taken")), dev(np.stack([cases[i]["grid"] for i in order]))
+        d_koff, d_qoff = dev(koff), dev(qoff)
+        d_out = torch.zeros(int(qoff[-1]) * 28, dtype=torch.uint8, device="cuda")
+        torch.cuda.synchronize()
+        # check_orientation differs between the cases (the frame-to-frame ones have it): one launch per setting, compare the frames it belongs to
+        for ori in (False, True):
+            P.search_by_projection_device(len(order), maxkp, d_kps.data_ptr(), d_desc.data_ptr(), d_koff.data_ptr(), d_grid.data_ptr(), d_q.data_ptr(),
+                                          d_qd.data_ptr(), d_qoff.data_ptr(), d_out.data_ptr(), d_u_right=d_ur.data_ptr(), d_taken_in=d_tk.data_ptr(),
+                                          check_orientation=ori)
+            torch.cuda.synchronize()
+            out = d_out.cpu().numpy().view(P.PROJ_MATCH_DTYPE)
+            for f, i in enumerate(order):
+                if bool(cases[i]["check_orientation"][0]) == ori:
+                    assert np.array_equal(_as_matrix(out[qoff[f]:qoff[f + 1]]), _as_matrix(wants[i][0])), (maxkp, f, i)

@@ -39,6 +39,19 @@ for name, a, b in (("moved pairs", "pk", "pf"), ("same frame", "pk", "pk")):
     for _ in range(10): step(a, b)
     e1.record(); torch.cuda.synchronize()
     print("%-12s %.3f ms per %d pairs, %.0f matches per pair" % (name, e0.elapsed_time(e1) / 10, NP, nm.float().mean().item()), flush=True)
+NP1 = NP
+for NPX in (1, 8):
+    NP = NPX
+    for name, a, b in (("moved pairs", "pk", "pf"), ("same frame", "pk", "pk")):
+        for _ in range(3): step(a, b)
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(20): step(a, b)
+        e1.record(); torch.cuda.synchronize()
+        ra, rb = C.c_int(0), C.c_int(0)
+        L.orbfe_debug_bow_rounds(C.byref(ra), C.byref(rb))
+        print("%-12s %.3f ms per %d pairs on the device, rounds max %d" % (name, e0.elapsed_time(e1) / 20, NP, ra.value), flush=True)
+NP = NP1
 (d0, k0), (d1, k1) = frames[0], frames[1]
 for name, fa, fb in (("moved pair", 0, 1), ("same frame", 0, 0)):
     fn = lambda: B.search_by_bow(frames[fa][0], frames[fa][1], fvs[fa], None, frames[fb][0], frames[fb][1], fvs[fb], 50, 0.7, True)
