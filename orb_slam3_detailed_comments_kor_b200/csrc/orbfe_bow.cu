@@ -206,10 +206,10 @@ __global__ void __launch_bounds__(BOW_NT) k_bow_assemble(const int* __restrict__
  * the stamp of an earlier unresolved query.  Queries of different nodes never share a candidate, and inside a node only queries that
  * compete for a feature both could take wait for each other. */
 #define SB_NT 256
-/* SearchByBoW: one CTA of 1024 threads per pair, so that a single pair (one Tracking call) does not wait on 8 warps; measured against 256 and
- * 512 threads and against loading the candidates four at a time ahead of their use: this form is the fastest for one pair and within a few
- * percent of the best for 512 pairs.  The frame's descriptors in shared memory (in feature-vector order) changed nothing measurable. */
-#define SBW_NT 1024
+/* SearchByBoW: one CTA per pair.  1024 threads when the call has few pairs (up to two per SM), so that a single pair — one Tracking call — does
+ * not wait on 8 warps; 512 threads for batches: at 61 registers a 1024-thread CTA is alone on its SM, two 512-thread ones share it and the
+ * last wave of a batch is half as long.  Measured against 256 threads, against loading the candidates four at a time ahead of their use and
+ * against the frame's descriptors in shared memory (tools/exp/sb_variants.py): no gain from either. */
 #define SB_FREE 0xFFFFu      /* takenBy: nobody */
 #define SB_PENDING 0x8000u   /* takenBy: taken in the running round, visible from the next one */
 __device__ int g_sbRoundsMax, g_sbRoundsSum;   /* diagnostics: rounds of the last launches (orbfe_debug_bow_rounds) */
@@ -221,6 +221,7 @@ struct SbSmem {
     int rot[32];
 };
 
+template <int SBW_NT>
 __global__ void __launch_bounds__(SBW_NT) k_search_by_bow(int maxF, const int* __restrict__ pairKf, const int* __restrict__ pairF, const uint4* __restrict__ desc,
                                                          const orbfe_keypoint* __restrict__ kps, int rowStride, const int* __restrict__ fvNodes,
                                                          const int* __restrict__ fvStarts, const int* __restrict__ fvFeats, const int* __restrict__ fvCount,
@@ -732,7 +733,10 @@ int orbfe_search_by_bow_device(int device, int npairs, int max_features, const i
     if (max_features < 1 || max_features > BOW_MAXF || row_stride > BOW_MAXF) { orbfe_set_error("at most %d features per frame", BOW_MAXF); return ORBFE_E_CAPACITY; }
     if ((uintptr_t)d_desc & 15) { orbfe_set_error("descriptor array must be 16-byte aligned"); return ORBFE_E_INVALID; }
     ORBFE_CUDA(cudaSetDevice(device));
-    k_search_by_bow<<<npairs, SBW_NT, 0, (cudaStream_t)stream>>>(max_features, d_pair_kf, d_pair_f, (const uint4*)d_desc, d_kps, row_stride, d_fv_nodes, d_fv_starts,
+    int sms = 0;
+    ORBFE_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+    const bool few = npairs <= 2 * sms;
+    (few ? k_search_by_bow<1024> : k_search_by_bow<512>)<<<npairs, few ? 1024 : 512, 0, (cudaStream_t)stream>>>(max_features, d_pair_kf, d_pair_f, (const uint4*)d_desc, d_kps, row_stride, d_fv_nodes, d_fv_starts,
                                                                 d_fv_feats, d_fv_count, d_has_map_point, d_n_left, th_low, nnratio, check_orientation ? 1 : 0, kf_kf ? 1 : 0, d_match_f,
                                                                 d_kf_out, d_nmatches);
     ORBFE_CUDA(cudaGetLastError());
