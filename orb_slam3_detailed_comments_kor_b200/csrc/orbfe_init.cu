@@ -20,7 +20,7 @@
 
 #include "orbfe_internal.h"
 
-#define SI_NT 512
+#define SI_NT 1024
 #define SI_MAXKP 8192   /* Tracking's initial extractor asks for 5 x nFeatures (src/Tracking.cc:1151-1157) */
 #define SI_COLS 64
 #define SI_ROWS 48
