@@ -200,6 +200,64 @@ __global__ void __launch_bounds__(256) k_clahe_apply(const uint8_t* __restrict__
         for (int k = 0; k < 4 && x0 + k < W; k++) dp[k] = (uint8_t)(out >> (8 * k));
 }
 
+/* The same blend for the usual shapes (width a multiple of 4, word-aligned frames, at most 16 tiles across, tiles at least 32 rows high),
+ * arranged so that a pixel costs its arithmetic and little else.  One CTA = 256 columns x 32 rows.  It first copies the tables it can
+ * touch into shared memory, one 256-byte slot per (tile row, tile column) with the clamping of the reference's tx1/tx2/ty1/ty2 built
+ * into the copy: slot (r, c) holds tile (clamp(ty0 + r), clamp(c - 1)), so that the four tables of a pixel are at a, a + 256, a + STRIDE,
+ * a + STRIDE + 256 for one address a — four loads with constant offsets.  A thread owns four adjacent columns (their x weights and table
+ * columns are computed once) and walks down eight rows. */
+#define CL_BW 64            /* threads across: 64 words = 256 columns */
+#define CL_BH 4             /* threads down */
+#define CL_ROWS 32          /* rows per CTA */
+#define CL_MAXTX 16
+#define CL_STRIDE ((CL_MAXTX + 2) * 256)   /* slot columns 0 .. tilesX + 1: raw tx1 = -1 .. tilesX - 1 and the column after it */
+#define CL_SLOTROWS 4       /* tile rows a 32-row band can touch (tiles >= 32 rows high: at most three), plus one */
+__global__ void __launch_bounds__(CL_BW * CL_BH) k_clahe_apply_band(const uint8_t* __restrict__ src, const uint8_t* __restrict__ lut, uint8_t* __restrict__ dst,
+                                                                    int W, int H, int tilesX, int tilesY, float invTw, float invTh) {
+    __shared__ __align__(16) uint8_t s_lut[CL_SLOTROWS * CL_STRIDE];
+    const int tid = threadIdx.y * CL_BW + threadIdx.x;
+    const int yb = blockIdx.y * CL_ROWS, yend = min(yb + CL_ROWS, H);
+    const size_t frame = (size_t)blockIdx.z * W * H;
+    const uint8_t* l = lut + (size_t)blockIdx.z * tilesX * tilesY * 256;
+    const int ty0 = __float2int_rd(__fsub_rn(__fmul_rn((float)yb, invTh), 0.5f));             /* raw ty1 of the band's first row, >= -1 */
+    const int nr = __float2int_rd(__fsub_rn(__fmul_rn((float)(yend - 1), invTh), 0.5f)) + 1 - ty0 + 1;   /* slot rows in use */
+    for (int i = tid; i < nr * (tilesX + 2) * 16; i += CL_BW * CL_BH) {
+        const int q = i & 15, sc = (i >> 4) % (tilesX + 2), sr = (i >> 4) / (tilesX + 2);
+        const int ty = min(max(ty0 + sr, 0), tilesY - 1), tx = min(max(sc - 1, 0), tilesX - 1);
+        reinterpret_cast<uint4*>(s_lut + sr * CL_STRIDE + sc * 256)[q] = __ldg(reinterpret_cast<const uint4*>(l + ((size_t)ty * tilesX + tx) * 256) + q);
+    }
+    const int x0 = (blockIdx.x * CL_BW + threadIdx.x) * 4;
+    int col[4];
+    float xa[4], xa1[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const float txf = __fsub_rn(__fmul_rn((float)(x0 + k), invTw), 0.5f);
+        const int tx1 = __float2int_rd(txf);
+        xa[k] = __fsub_rn(txf, (float)tx1);
+        xa1[k] = __fsub_rn(1.0f, xa[k]);
+        col[k] = (min(tx1, tilesX - 1) + 1) * 256;      /* columns beyond the image are never used; keep the address inside the row of slots */
+    }
+    __syncthreads();
+    if (x0 >= W) return;
+    for (int y = yb + threadIdx.y; y < yend; y += CL_BH) {
+        const float tyf = __fsub_rn(__fmul_rn((float)y, invTh), 0.5f);
+        const int ty1 = __float2int_rd(tyf);
+        const float ya = __fsub_rn(tyf, (float)ty1), ya1 = __fsub_rn(1.0f, ya);
+        const uint8_t* row = s_lut + (ty1 - ty0) * CL_STRIDE;
+        const uint32_t in = *reinterpret_cast<const uint32_t*>(src + frame + (size_t)y * W + x0);
+        uint32_t out = 0;
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const uint8_t* t = row + col[k] + ((in >> (8 * k)) & 255);
+            const float a = (float)t[0], b = (float)t[256], c = (float)t[CL_STRIDE], d = (float)t[CL_STRIDE + 256];
+            const float top = __fadd_rn(__fmul_rn(a, xa1[k]), __fmul_rn(b, xa[k])), bot = __fadd_rn(__fmul_rn(c, xa1[k]), __fmul_rn(d, xa[k]));
+            const int r = __float2int_rn(__fadd_rn(__fmul_rn(top, ya1), __fmul_rn(bot, ya)));
+            out |= (uint32_t)min(max(r, 0), 255) << (8 * k);
+        }
+        *reinterpret_cast<uint32_t*>(dst + frame + (size_t)y * W + x0) = out;
+    }
+}
+
 extern "C" {
 
 void orbfe_clahe_destroy(orbfe_clahe* c) {
@@ -248,7 +306,11 @@ int orbfe_clahe_apply_batch_device(orbfe_clahe* c, const uint8_t* d_src, uint8_t
     cudaStream_t st = stream ? (cudaStream_t)stream : c->stream;
     k_clahe_lut<<<dim3(c->tilesX * c->tilesY, nframes), 256, 0, st>>>(d_src, c->dLut, c->W, c->H, c->tilesX, c->tw, c->th, c->clipLimit, c->lutScale);
     const int gpr = (c->W + 3) / 4;
-    k_clahe_apply<<<dim3((gpr * c->H + 255) / 256, nframes), 256, 0, st>>>(d_src, c->dLut, d_dst, c->W, c->H, c->tilesX, c->tilesY, c->invTw, c->invTh, gpr);
+    if ((c->W & 3) == 0 && (((uintptr_t)d_src | (uintptr_t)d_dst) & 3) == 0 && c->tilesX <= CL_MAXTX && c->th >= CL_ROWS && nframes <= 65535)
+        k_clahe_apply_band<<<dim3((gpr + CL_BW - 1) / CL_BW, (c->H + CL_ROWS - 1) / CL_ROWS, nframes), dim3(CL_BW, CL_BH), 0, st>>>(
+            d_src, c->dLut, d_dst, c->W, c->H, c->tilesX, c->tilesY, c->invTw, c->invTh);
+    else
+        k_clahe_apply<<<dim3((gpr * c->H + 255) / 256, nframes), 256, 0, st>>>(d_src, c->dLut, d_dst, c->W, c->H, c->tilesX, c->tilesY, c->invTw, c->invTh, gpr);
     ORBFE_CUDA(cudaGetLastError());
     return ORBFE_OK;
 }

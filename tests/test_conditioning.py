@@ -132,6 +132,15 @@ def test_gpu_clahe_matches_oracle_and_cv2():
         assert np.array_equal(c.lut(0), lut), name + ": lookup tables"
         assert np.array_equal(out, ref) and _same(out, want), name
         c.close()
+    # shapes that reach the banded kernel with padding in both directions, the most tiles across it takes, and one more (the general kernel)
+    rng = np.random.RandomState(3)
+    for (h, w), clip, tiles in (((470, 644), 3.0, (8, 8)), ((480, 752), 2.0, (16, 4)), ((331, 680), 4.0, (17, 10)), ((97, 256), 3.0, (2, 3))):
+        src = np.clip(rng.normal(110, 50, (h, w)) + 40 * np.sin(np.arange(w) / 37.0)[None, :] + 30 * np.cos(np.arange(h) / 23.0)[:, None], 0, 255).astype(np.uint8)
+        c = CLAHE(w, h, clip, tiles)
+        ref, lut = O.clahe(src, clip, tiles, return_lut=True)
+        assert np.array_equal(c.apply(src), ref), ((h, w), tiles)
+        assert np.array_equal(c.lut(0), lut), ((h, w), tiles, "lookup tables")
+        c.close()
     # a TUM-VI sized batch, device to device, in place, frames at different brightness
     W = H = 512
     frames = []
