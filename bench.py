@@ -1177,6 +1177,9 @@ def main():
         one_call = {}
         for name, gpu_fn, cpu_fn in (
                 ("extract", lambda: exL(img0, (0, 0)), lambda: cpu_ex(img0, (0, 0))),
+                ("stereo_frame", lambda: M.stereo_frames_batch_host(exL, exR, hLn[:1], hRn[:1], MBF, 0.0, FX, (0, 0)),
+                 (lambda: cpu_ex.stereo(img0, np.ascontiguousarray(hRn[0]), MBF, float(np.float32(MBF) / np.float32(FX)))) if reference_available() else None),
+                ("compute_bow", lambda: voc.transform(bsample[0], 4), lambda: ovoc.transform(bsample[0], 4)),
                 ("search_by_projection", lambda: PJ.search_by_projection(c0["kps"], c0["desc"], c0["queries"], c0["qdesc"], c0["grid"], u_right=c0["u_right"], taken=c0["taken"]),
                  lambda: O.search_by_projection(c0["kps"], c0["desc"], c0["queries"], c0["qdesc"], c0["grid"], u_right=c0["u_right"], taken=c0["taken"])),
                 ("search_by_projection_last_frame",
@@ -1191,7 +1194,7 @@ def main():
                                                     scale8 * scale8, 50, False, False, True)),
                 ("search_for_initialization", lambda: PJ.search_for_initialization(*[a.copy() if hasattr(a, "copy") else a for a in i0[:6]], 100, 0.9, True),
                  lambda: init_fn(*[a.copy() if hasattr(a, "copy") else a for a in i0[:6]], 100, 0.9, True))):
-            one_call[name] = {"gpu_host_call_ms": med_ms(gpu_fn, 20), "cpu_one_thread_ms": med_ms(cpu_fn, 3)}
+            one_call[name] = {"gpu_host_call_ms": med_ms(gpu_fn, 20), "cpu_one_thread_ms": med_ms(cpu_fn, 3) if cpu_fn else None}
         cpu["one_call_latency"] = one_call
         cpu["one_call_latency_note"] = ("median wall time of ONE call of the host entry point a shim makes (host arrays in, host arrays out, copies included, Python "
                                         "ctypes glue on both sides) beside the CPU oracle / reference on one thread with the same inputs; extract = one 752x480 "

@@ -22,4 +22,4 @@ for l in sys.stdin:
     print("consumers", d.get("consumers"))
     print("cpu consumers", {k: (d.get("cpu_baseline") or {}).get(k) for k in ("search_by_bow", "search_for_triangulation", "distinctive_descriptors", "initialization")})
     for k, v in ((d.get("cpu_baseline") or {}).get("one_call_latency") or {}).items():
-        print("one call %-34s gpu host call %.3f ms | cpu one thread %.3f ms" % (k, v["gpu_host_call_ms"], v["cpu_one_thread_ms"]))
+        print("one call %-34s gpu host call %.3f ms | cpu one thread %s ms" % (k, v["gpu_host_call_ms"], "%.3f" % v["cpu_one_thread_ms"] if v["cpu_one_thread_ms"] else "-"))
