@@ -475,8 +475,6 @@ int orbfe_search_by_projection_device(int device, int nframes, int max_keypoints
                                       const float* d_inv_level_sigma2, orbfe_proj_match* d_out, uint8_t* d_taken_out, void* stream);
 /* Diagnostics (synchronises the device): maximum and sum over the frames of the speculative rounds the projection kernel needed since the last call. */
 int orbfe_debug_projection_rounds(int* max_rounds, int* sum_rounds);
-/* The same for the SearchByBoW kernel (maximum and sum over the pairs). */
-int orbfe_debug_bow_rounds(int* max_rounds, int* sum_rounds);
 /* One frame over host memory (copies inside, synchronous).  taken is updated in place (may be NULL); *nmatches receives the
  * reference's return value (an accepted row with a stereo partner counts twice). */
 int orbfe_search_by_projection(int device, const orbfe_keypoint* kps, const uint8_t* desc, int n, int n_left, const float* u_right,

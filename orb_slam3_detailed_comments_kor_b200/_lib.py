@@ -109,7 +109,6 @@ SIGNATURES = {
     "orbfe_fisheye_stereo_frames": (i32, [vp, vp, i32, vp, C.c_double, vp, vp, vp, vp, i32]),
     "orbfe_fisheye_frames_submit": (i32, [vp, vp, vp, vp, i32, i32, i32, vp, C.c_double, vp, vp, vp, vp, i32, vp, vp, vp, vp]),
     "orbfe_debug_projection_rounds": (i32, [C.POINTER(i32), C.POINTER(i32)]),
-    "orbfe_debug_bow_rounds": (i32, [C.POINTER(i32), C.POINTER(i32)]),
     "orbfe_search_by_projection": (i32, [i32, vp, vp, i32, i32, vp, vp, vp, vp, vp, vp, i32, i32, C.c_float, i32, vp, vp, C.POINTER(i32)]),
     "orbfe_clahe_create": (i32, [i32, i32, i32, C.c_double, i32, i32, i32, C.POINTER(vp)]),
     "orbfe_clahe_destroy": (None, [vp]),

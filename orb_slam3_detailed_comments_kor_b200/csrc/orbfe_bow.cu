@@ -200,26 +200,19 @@ __global__ void __launch_bounds__(BOW_NT) k_bow_assemble(const int* __restrict__
  * a map point scans the frame's features of the node that are still unmatched (best / second best with the strict `<` rule),
  * and takes the best one if bestDist1 <= TH_LOW and (float)bestDist1 < mfNNratio * (float)bestDist2; then the rotation histogram
  * (ComputeThreeMaxima) removes the matches outside the three fullest bins.
- * One CTA = one (keyframe, frame) pair.  The serial "already matched" rule is reproduced exactly by the speculative rounds of
- * orbfe_project.cu: a query (one keyframe feature, in feature-vector order) stamps the unmatched frame features of its node,
- * that it could take (distance <= TH_LOW), scans them, and becomes final iff no candidate at or below its second-best distance carries
- * the stamp of an earlier unresolved query.  Queries of different nodes never share a candidate, and inside a node only queries that
- * compete for a feature both could take wait for each other. */
+ * One CTA = one (keyframe, frame) pair; one warp = one vocabulary node at a time (the warps of the CTA draw nodes from a counter).
+ * The serial "already matched" rule only ties together the queries of ONE node — a frame feature sits in exactly one node of the frame's
+ * feature vector, so queries of different nodes never share a candidate — which makes the reference's loop over a node a job for a
+ * warp that simply runs it in order: for each keyframe feature of the node in turn, the lanes scan the node's frame features in
+ * parallel (lane l takes candidates l, l + 32, ...), a butterfly merges the lanes' (best, first index of the best, second best) — the
+ * serial scan's strict `<` updates give exactly the smallest distance, its first position, and the second smallest value of the
+ * multiset — and lane 0 decides and marks the taken feature before the next query starts.  When the node's run in the frame has at
+ * most 32 features (the usual case: ~12) every lane keeps its candidate's descriptor in registers for the whole node.
+ * (Round 2 first ran this as speculative rounds over all queries of the pair, as orbfe_project.cu does: there, windows overlap
+ * arbitrarily; here the independence of the nodes gives the serial order for free, and a pair costs microseconds instead of rounds of
+ * barriers: one pair of 1500 x 1500 features with 30-deep chains 0.55 -> 0.057 ms, 512 such pairs 2.0 -> 0.2 ms.)
+ * 1024 threads for a call with few pairs (up to two per SM), 512 for batches (256 measured: 5 % slower). */
 #define SB_NT 256
-/* SearchByBoW: one CTA per pair.  1024 threads when the call has few pairs (up to two per SM), so that a single pair — one Tracking call — does
- * not wait on 8 warps; 512 threads for batches: at 61 registers a 1024-thread CTA is alone on its SM, two 512-thread ones share it and the
- * last wave of a batch is half as long.  Measured against 256 threads, against loading the candidates four at a time ahead of their use and
- * against the frame's descriptors in shared memory (tools/exp/sb_variants.py): no gain from either. */
-#define SB_FREE 0xFFFFu      /* takenBy: nobody */
-#define SB_PENDING 0x8000u   /* takenBy: taken in the running round, visible from the next one */
-__device__ int g_sbRoundsMax, g_sbRoundsSum;   /* diagnostics: rounds of the last launches (orbfe_debug_bow_rounds) */
-struct SbSmem {
-    int owner[BOW_MAXF];
-    uint32_t range[BOW_MAXF];          /* per query: first | last+1 << 16 of its node's run in the frame's fvFeats (0 = none) */
-    uint16_t takenBy[BOW_MAXF];        /* per frame feature: 1 + the query that took it (0: occupied before the search), SB_FREE, | SB_PENDING */
-    uint32_t state[BOW_MAXF / 4];      /* per query: 0 unresolved, 1 resolved */
-    int rot[32];
-};
 
 template <int SBW_NT>
 __global__ void __launch_bounds__(SBW_NT) k_search_by_bow(int maxF, const int* __restrict__ pairKf, const int* __restrict__ pairF, const uint4* __restrict__ desc,
@@ -228,106 +221,108 @@ __global__ void __launch_bounds__(SBW_NT) k_search_by_bow(int maxF, const int* _
                                                          const uint8_t* __restrict__ hasMp, const int* __restrict__ nLeftAll, int thLow, float nnratio,
                                                          int checkOri, int kfkf, int* __restrict__ matchF, orbfe_match* __restrict__ kfOut,
                                                          int* __restrict__ nmatches) {
-    __shared__ SbSmem s;
-    const int tid = threadIdx.x, pr = blockIdx.x;
+    __shared__ uint8_t s_taken[BOW_MAXF];     /* per frame feature: matched already (vpMapPointMatches[realIdxF] != NULL) */
+    __shared__ int s_rot[32];
+    __shared__ int s_next;
+    const int tid = threadIdx.x, lane = tid & 31, pr = blockIdx.x;
     const int a = pairKf[pr], b = pairF[pr];
     const int* nodesA = fvNodes + (size_t)a * maxF; const int* startsA = fvStarts + (size_t)a * (maxF + 1); const int* featsA = fvFeats + (size_t)a * maxF;
     const int* nodesB = fvNodes + (size_t)b * maxF; const int* startsB = fvStarts + (size_t)b * (maxF + 1); const int* featsB = fvFeats + (size_t)b * maxF;
     const int nnA = fvCount[a], nnB = fvCount[b];
     const int nLeftF = (nLeftAll && !kfkf) ? nLeftAll[b] : -1;   /* F.Nleft: rows >= it belong to the right camera of a fisheye rig */
-    const int nq = nnA ? startsA[nnA] : 0;                       /* keyframe features that sit in the feature vector */
     const uint4* descA = desc + (size_t)a * rowStride * 2; const uint4* descB = desc + (size_t)b * rowStride * 2;
+    const uint8_t* mpA = hasMp ? hasMp + (size_t)a * rowStride : nullptr;
     int* mF = matchF + (size_t)pr * rowStride;
     orbfe_match* ko = kfOut ? kfOut + (size_t)pr * rowStride : nullptr;
-    uint8_t* stateB = reinterpret_cast<uint8_t*>(s.state);
     for (int i = tid; i < rowStride; i += SBW_NT) { mF[i] = -1; if (ko) { orbfe_match m; m.best1 = 256; m.best2 = 256; m.idx = -1; m.accepted = 0; ko[i] = m; } }
-    for (int i = tid; i < BOW_MAXF / 4; i += SBW_NT) s.state[i] = 0;
     /* keyframe-keyframe variant: rows of the second keyframe without a map point are never candidates (:886-892) */
-    for (int i = tid; i < BOW_MAXF; i += SBW_NT) s.takenBy[i] = (kfkf && hasMp && i < rowStride && !hasMp[(size_t)b * rowStride + i]) ? 0 : SB_FREE;
+    for (int i = tid; i < BOW_MAXF; i += SBW_NT) s_taken[i] = (kfkf && hasMp && i < rowStride && !hasMp[(size_t)b * rowStride + i]) ? 1 : 0;
+    if (tid == 0) s_next = 0;
     __syncthreads();
-    /* the node of every query, and that node's run in the frame's feature vector (the lockstep walk of :290-420 is a merge join) */
-    for (int e = tid; e < nnA; e += SBW_NT) {
+    /* (best1 << 16 | position of the first best, best2) of two candidate sets -> of their union */
+#define SB_MERGE(k1, b2, ok1, ob2)                                                \
+    do {                                                                          \
+        const unsigned lo_ = min(k1, ok1), hi_ = max(k1, ok1);                     \
+        b2 = min(min(b2, ob2), (int)(hi_ >> 16));                                  \
+        k1 = lo_;                                                                  \
+    } while (0)
+    for (;;) {
+        int e = 0;
+        if (lane == 0) e = atomicAdd(&s_next, 1);
+        e = __shfl_sync(0xffffffffu, e, 0);
+        if (e >= nnA) break;
+        /* the lockstep walk of :290-420 is a merge join: the node's run in the frame's feature vector by binary search */
         const int node = nodesA[e];
         int lo = 0, hi = nnB;
         while (lo < hi) { const int mid = (lo + hi) >> 1; if (nodesB[mid] < node) lo = mid + 1; else hi = mid; }
-        const uint32_t rg = (lo < nnB && nodesB[lo] == node) ? ((uint32_t)startsB[lo] | ((uint32_t)startsB[lo + 1] << 16)) : 0u;
-        for (int j = startsA[e]; j < startsA[e + 1]; j++) {
-            const int row = featsA[j];
-            const bool live = rg != 0 && (!hasMp || hasMp[(size_t)a * rowStride + row]);   /* pMP && !pMP->isBad() */
-            s.range[j] = live ? rg : 0u;
-            if (!live) stateB[j] = 1;
-        }
-    }
-    __syncthreads();
-    /* Rounds.  A frame feature counts as matched for query q iff a query BEFORE q took it (or it was occupied from the start): queries
-     * become final out of order, and an earlier one must not see what a later one took.
-     * A query can only ever take a frame feature at a distance <= TH_LOW (whatever earlier queries do to its candidate set, the feature
-     * it takes is its best one, and that must pass the threshold): only those get its stamp.  With stamps on the node's whole run the
-     * queries of a node would resolve one per round even when nothing matches. */
-#define SB_TAKEN_FOR(row, q) ((unsigned)s.takenBy[row] <= (unsigned)(q))   /* stored q' + 1 <= q  <=>  q' < q; pending and free values are >= 0x8000 */
-    int rounds = 0;
-    for (;;) {
-        for (int i = tid; i < maxF; i += SBW_NT) {
-            s.owner[i] = INT_MAX;
-            const unsigned v = s.takenBy[i];
-            if ((v & SB_PENDING) && v != SB_FREE) s.takenBy[i] = (uint16_t)(v & ~SB_PENDING);
-        }
-        __syncthreads();
-#define SB_SCAN(BODY)                                                                                                  \
-        for (int j = rg & 0xFFFF, j1 = (int)(rg >> 16); j < j1; j++) {                                                     \
-            const int row = featsB[j];                                                                                     \
-            if (SB_TAKEN_FOR(row, q)) continue;                   /* if(vpMapPointMatches[realIdxF]) continue; */          \
-            const int dist = bow_ham(qa, qb, __ldg(descB + 2 * row), __ldg(descB + 2 * row + 1));                          \
-            BODY                                                                                                           \
-        }
-        for (int q = tid; q < nq; q += SBW_NT) {
-            if (stateB[q]) continue;
-            const uint32_t rg = s.range[q];
+        if (lo >= nnB || nodesB[lo] != node) continue;
+        const int j0 = startsB[lo], run = startsB[lo + 1] - j0;
+        const int qBeg = startsA[e], qEnd = startsA[e + 1];
+        if (run <= 0) continue;
+        /* my candidate when the run fits the warp: row and descriptor stay in registers for all the node's queries */
+        const bool small = run <= 32;
+        int myRow = -1;
+        uint4 ca = make_uint4(0, 0, 0, 0), cb = ca;
+        if (small && lane < run) { myRow = featsB[j0 + lane]; ca = __ldg(descB + 2 * myRow); cb = __ldg(descB + 2 * myRow + 1); }
+        for (int q = qBeg; q < qEnd; q++) {
             const int rowA = featsA[q];
+            if (mpA && !mpA[rowA]) continue;                               /* pMP && !pMP->isBad() */
             const uint4 qa = __ldg(descA + 2 * rowA), qb = __ldg(descA + 2 * rowA + 1);
-            SB_SCAN(if (dist <= thLow) atomicMin(&s.owner[row], q);)
-        }
-        __syncthreads();
-        int pending = 0;
-        for (int q = tid; q < nq; q += SBW_NT) {
-            if (stateB[q]) continue;
-            const uint32_t rg = s.range[q];
-            const int rowA = featsA[q];
-            const uint4 qa = __ldg(descA + 2 * rowA), qb = __ldg(descA + 2 * rowA + 1);
-            int best1 = 256, best2 = 256, bestIdx = -1;
-            int best1R = 256, best2R = 256, bestIdxR = -1;        /* fisheye rig: the frame's right-camera rows compete separately (:330-358) */
-            int foreign = 257;                                    /* the closest candidate that carries the stamp of an earlier unresolved query */
-            SB_SCAN(
-                if (nLeftF < 0 || row < nLeftF) {
-                    if (dist < best1) { best2 = best1; best1 = dist; bestIdx = row; }
-                    else if (dist < best2) best2 = dist;
-                } else {
-                    if (dist < best1R) { best2R = best1R; best1R = dist; bestIdxR = row; }
-                    else if (dist < best2R) best2R = dist;
+            unsigned k1 = 0xFFFFFFFFu, k1R = 0xFFFFFFFFu;                   /* 256 << 16 | 0xFFFF would do; all ones = nothing seen */
+            int b2 = 256, b2R = 256;
+            if (small) {
+                if (myRow >= 0 && !s_taken[myRow]) {                       /* if(vpMapPointMatches[realIdxF]) continue; */
+                    const unsigned key = ((unsigned)bow_ham(qa, qb, ca, cb) << 16) | (unsigned)lane;
+                    if (nLeftF < 0 || myRow < nLeftF) k1 = key; else k1R = key;
                 }
-                if (s.owner[row] < q) foreign = min(foreign, dist);)
-            const int reach = nLeftF < 0 ? best2 : max(best2, best2R);
-            if (foreign <= reach) { pending++; continue; }
+            } else {
+                for (int c = lane; c < run; c += 32) {
+                    const int row = featsB[j0 + c];
+                    if (s_taken[row]) continue;
+                    const int dist = bow_ham(qa, qb, __ldg(descB + 2 * row), __ldg(descB + 2 * row + 1));
+                    const unsigned key = ((unsigned)dist << 16) | (unsigned)c;
+                    if (nLeftF < 0 || row < nLeftF) { if (key < k1) { b2 = min(b2, (int)(k1 >> 16)); k1 = key; } else b2 = min(b2, dist); }
+                    else { if (key < k1R) { b2R = min(b2R, (int)(k1R >> 16)); k1R = key; } else b2R = min(b2R, dist); }
+                }
+            }
+#pragma unroll
+            for (int o = 16; o; o >>= 1) {
+                const unsigned ok1 = __shfl_xor_sync(0xffffffffu, k1, o);
+                const int ob2 = __shfl_xor_sync(0xffffffffu, b2, o);
+                SB_MERGE(k1, b2, ok1, ob2);
+            }
+            if (nLeftF >= 0) {
+#pragma unroll
+                for (int o = 16; o; o >>= 1) {
+                    const unsigned ok1 = __shfl_xor_sync(0xffffffffu, k1R, o);
+                    const int ob2 = __shfl_xor_sync(0xffffffffu, b2R, o);
+                    SB_MERGE(k1R, b2R, ok1, ob2);
+                }
+            }
+            /* all lanes hold the same result; lane 0 writes */
+            const int best1 = min((int)(k1 >> 16), 256), best2 = min(b2, 256);
+            const int bestIdx = k1 == 0xFFFFFFFFu ? -1 : featsB[j0 + (int)(k1 & 0xFFFFu)];
+            const int best1R = min((int)(k1R >> 16), 256);
+            const int bestIdxR = k1R == 0xFFFFFFFFu ? -1 : featsB[j0 + (int)(k1R & 0xFFFFu)];
             const bool th1 = bestIdx >= 0 && (kfkf ? best1 < thLow : best1 <= thLow);
             const bool ok = th1 && (float)best1 < nnratio * (float)best2;
             /* :388-416: inside `if(bestDist1<=TH_LOW)`, the right-camera best is taken whenever it is <= TH_LOW (`|| true`) */
             const bool okR = !kfkf && nLeftF >= 0 && th1 && bestIdxR >= 0 && best1R <= thLow;
-            stateB[q] = 1;
-            if (ko) { orbfe_match m; m.best1 = best1; m.best2 = best2; m.idx = bestIdx; m.accepted = ok ? 1 : 0; ko[rowA] = m; }
-            if (ok) { mF[bestIdx] = rowA; s.takenBy[bestIdx] = (uint16_t)((q + 1) | SB_PENDING); }
-            if (okR) { mF[bestIdxR] = rowA; s.takenBy[bestIdxR] = (uint16_t)((q + 1) | SB_PENDING); }
+            if (lane == 0) {
+                if (ko) { orbfe_match m; m.best1 = best1; m.best2 = best2; m.idx = bestIdx; m.accepted = ok ? 1 : 0; ko[rowA] = m; }
+                if (ok) { mF[bestIdx] = rowA; s_taken[bestIdx] = 1; }
+                if (okR) { mF[bestIdxR] = rowA; s_taken[bestIdxR] = 1; }
+            }
+            __syncwarp();
         }
-        rounds++;
-        if (__syncthreads_count(pending) == 0) break;
     }
-    if (tid == 0) { atomicMax(&g_sbRoundsMax, rounds); atomicAdd(&g_sbRoundsSum, rounds); }
-#undef SB_SCAN
-#undef SB_TAKEN_FOR
+#undef SB_MERGE
+    __syncthreads();
     /* rotation consistency (:368-384, 440-458) */
     if (checkOri) {
         const float factor = 1.0f / 30.0f;
         const orbfe_keypoint* kA = kps + (size_t)a * rowStride; const orbfe_keypoint* kB = kps + (size_t)b * rowStride;
-        if (tid < 32) s.rot[tid] = 0;
+        if (tid < 32) s_rot[tid] = 0;
         __syncthreads();
         for (int i = tid; i < rowStride; i += SBW_NT) {
             const int ra = mF[i];
@@ -336,23 +331,23 @@ __global__ void __launch_bounds__(SBW_NT) k_search_by_bow(int maxF, const int* _
             if (rot < 0.0f) rot += 360.0f;
             int bin = (int)roundf(rot * factor);
             if (bin == 30) bin = 0;
-            if (bin >= 0 && bin < 30) atomicAdd(&s.rot[bin], 1);
+            if (bin >= 0 && bin < 30) atomicAdd(&s_rot[bin], 1);
         }
         __syncthreads();
         if (tid == 0) {
             int ind1 = -1, ind2 = -1, ind3 = -1, max1 = 0, max2 = 0, max3 = 0;
             for (int i = 0; i < 30; i++) {
-                const int c = s.rot[i];
+                const int c = s_rot[i];
                 if (c > max1) { max3 = max2; max2 = max1; max1 = c; ind3 = ind2; ind2 = ind1; ind1 = i; }
                 else if (c > max2) { max3 = max2; max2 = c; ind3 = ind2; ind2 = i; }
                 else if (c > max3) { max3 = c; ind3 = i; }
             }
             if ((float)max2 < 0.1f * (float)max1) { ind2 = -1; ind3 = -1; }
             else if ((float)max3 < 0.1f * (float)max1) { ind3 = -1; }
-            s.rot[30] = ind1; s.rot[31] = (ind2 & 0xFF) | ((ind3 & 0xFF) << 8);
+            s_rot[30] = ind1; s_rot[31] = (ind2 & 0xFF) | ((ind3 & 0xFF) << 8);
         }
         __syncthreads();
-        const int ind1 = s.rot[30], ind2 = (int)(signed char)(s.rot[31] & 0xFF), ind3 = (int)(signed char)((s.rot[31] >> 8) & 0xFF);
+        const int ind1 = s_rot[30], ind2 = (int)(signed char)(s_rot[31] & 0xFF), ind3 = (int)(signed char)((s_rot[31] >> 8) & 0xFF);
         for (int i = tid; i < rowStride; i += SBW_NT) {
             const int ra = mF[i];
             if (ra < 0) continue;
@@ -708,19 +703,6 @@ int orbfe_bow_device_views(orbfe_vocabulary* v, const int32_t** d_feat_word, con
     if (d_fv_starts) *d_fv_starts = v->fvStarts;
     if (d_fv_feats) *d_fv_feats = v->fvFeats;
     if (d_fv_count) *d_fv_count = v->fvCount;
-    return ORBFE_OK;
-}
-
-/* diagnostics: maximum and sum over the CTAs (pairs) of the rounds k_search_by_bow needed since the last call; resets both */
-int orbfe_debug_bow_rounds(int* max_rounds, int* sum_rounds) {
-    int z = 0, a = 0, b = 0;
-    ORBFE_CUDA(cudaDeviceSynchronize());
-    ORBFE_CUDA(cudaMemcpyFromSymbol(&a, g_sbRoundsMax, sizeof a));
-    ORBFE_CUDA(cudaMemcpyFromSymbol(&b, g_sbRoundsSum, sizeof b));
-    ORBFE_CUDA(cudaMemcpyToSymbol(g_sbRoundsMax, &z, sizeof z));
-    ORBFE_CUDA(cudaMemcpyToSymbol(g_sbRoundsSum, &z, sizeof z));
-    if (max_rounds) *max_rounds = a;
-    if (sum_rounds) *sum_rounds = b;
     return ORBFE_OK;
 }
 

@@ -48,9 +48,7 @@ for NPX in (1, 8):
         e0.record()
         for _ in range(20): step(a, b)
         e1.record(); torch.cuda.synchronize()
-        ra, rb = C.c_int(0), C.c_int(0)
-        L.orbfe_debug_bow_rounds(C.byref(ra), C.byref(rb))
-        print("%-12s %.3f ms per %d pairs on the device, rounds max %d" % (name, e0.elapsed_time(e1) / 20, NP, ra.value), flush=True)
+        print("%-12s %.3f ms per %d pairs on the device" % (name, e0.elapsed_time(e1) / 20, NP), flush=True)
 NP = NP1
 (d0, k0), (d1, k1) = frames[0], frames[1]
 for name, fa, fb in (("moved pair", 0, 1), ("same frame", 0, 0)):
