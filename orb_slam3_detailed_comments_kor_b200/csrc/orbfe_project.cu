@@ -110,9 +110,10 @@ static __device__ __forceinline__ int pj_ham(const uint4 qa, const uint4 qb, con
            __popc(qb.z ^ b.z) + __popc(qb.w ^ b.w);
 }
 
-/* Frame::GetFeaturesInArea: visit(row, octave) for every keypoint of the window, in the reference's order */
+/* Frame::GetFeaturesInArea: visit(row, octave, position in `sorted`) for every keypoint of the window, in the reference's order (ascending
+ * position in `sorted`: column by column, rows ascending inside a cell) */
 template <bool CACHE, class F>
-static __device__ __forceinline__ void pj_window(const PjFrame& fr, const PjSmem& s, const orbfe_proj_query& p, F&& visit) {
+static __device__ __forceinline__ void pj_window(const PjFrame& fr, const PjSmem& s, const orbfe_proj_query& p, int colFirst, int colStep, F&& visit) {
     const float r = p.radius, ax = p.x - fr.minx, ay = p.y - fr.miny;
     const int x0 = max(0, (int)floorf((ax - r) * fr.invw));
     if (x0 >= PJ_COLS) return;
@@ -124,7 +125,7 @@ static __device__ __forceinline__ void pj_window(const PjFrame& fr, const PjSmem
     if (y1 < 0) return;
     if ((p.flags & ORBFE_PQ_RIGHT) && fr.nLeft < 0) return;   /* no right camera: mGridRight is empty (and not even allocated here) */
     const int side = (p.flags & ORBFE_PQ_RIGHT) ? PJ_CELLS : 0;
-    for (int ix = x0; ix <= x1; ix++) {
+    for (int ix = x0 + colFirst; ix <= x1; ix += colStep) {   /* a group of colStep lanes shares a window: lane colFirst takes every colStep-th column */
         const int c0 = side + ix * PJ_ROWS + y0, c1 = side + ix * PJ_ROWS + y1;
         /* the cells iy = y0..y1 of one column are adjacent in the sort: one run */
         const int beg = c0 ? s.cellEnd[c0 - 1] : 0, end = s.cellEnd[c1];
@@ -280,8 +281,39 @@ __global__ void __launch_bounds__(NT, MINB) k_search_by_projection(int maxKp, co
      * A round costs (participants x window); a query behind a long chain of earlier ones over the same keypoints would pay that
      * every round while it waits.  So only the earliest PJ_FRONT unresolved queries take part: the rule of step B needs the stamps
      * of all EARLIER unresolved queries, and those are inside the front by construction. */
-    __shared__ int s_front;
-    int myFirst = tid;   /* my first query that may still be unresolved (I own tid, tid + NT, ...) */
+    __shared__ int s_front, s_walked;
+    /* How many lanes share a query.  With the small windows of SearchLocalPoints (a handful of keypoints) one thread per query is the
+     * efficient form.  With the wide windows of the frame-to-frame search (th = 7 or 15 times the level scale: tens to hundreds of
+     * keypoints, and very unequal) a thread per query leaves most lanes of a warp waiting for the longest window, so eight lanes share
+     * a query, each taking every eighth grid column, and merge their results.  Decided per frame from the mean number of keypoints in
+     * the columns its queries walk. */
+    if (tid == 0) s_walked = 0;
+    __syncthreads();
+    {
+        int mine = 0;
+        for (int q = tid; q < nq; q += NT) {
+            const orbfe_proj_query p = qs[q];
+            if (p.flags & ORBFE_PQ_SKIP) continue;
+            const float r = p.radius, ax = p.x - fr.minx, ay = p.y - fr.miny;
+            const int x0 = max(0, (int)floorf((ax - r) * fr.invw)), x1 = min(PJ_COLS - 1, (int)ceilf((ax + r) * fr.invw));
+            const int y0 = max(0, (int)floorf((ay - r) * fr.invh)), y1 = min(PJ_ROWS - 1, (int)ceilf((ay + r) * fr.invh));
+            if (x0 >= PJ_COLS || x1 < 0 || y0 >= PJ_ROWS || y1 < 0 || ((p.flags & ORBFE_PQ_RIGHT) && fr.nLeft < 0)) continue;
+            const int side = (p.flags & ORBFE_PQ_RIGHT) ? PJ_CELLS : 0;
+            for (int ix = x0; ix <= x1; ix++) {
+                const int c0 = side + ix * PJ_ROWS + y0, c1 = side + ix * PJ_ROWS + y1;
+                mine += s.cellEnd[c1] - (c0 ? s.cellEnd[c0 - 1] : 0);
+            }
+        }
+#pragma unroll
+        for (int o = 16; o; o >>= 1) mine += __shfl_xor_sync(0xffffffffu, mine, o);
+        if ((tid & 31) == 0 && mine) atomicAdd(&s_walked, mine);
+    }
+    __syncthreads();
+    const int G = (nq > 0 && s_walked > 12 * nq) ? 8 : 1;       /* lanes per query */
+    const int gl = tid & (G - 1), NG = NT / G;                 /* my lane in the group, groups in the CTA */
+    const unsigned gmask = G == 1 ? (1u << (tid & 31)) : (0xFFu << (tid & 24));
+    const int leader = tid & 31 & ~(G - 1);
+    int myFirst = tid / G;   /* my group's first query that may still be unresolved (it owns myFirst, myFirst + NG, ...) */
     int rounds = 0;
     for (;;) {
         for (int i = tid; i < fr.n; i += NT) {
@@ -291,21 +323,21 @@ __global__ void __launch_bounds__(NT, MINB) k_search_by_projection(int maxKp, co
         }
         if (tid == 0) s_front = INT_MAX;
         __syncthreads();
-        while (myFirst < nq && status[myFirst * 7] != PJ_PENDING) myFirst += NT;
+        while (myFirst < nq && status[myFirst * 7] != PJ_PENDING) myFirst += NG;
         if (myFirst < nq) atomicMin(&s_front, myFirst);
         __syncthreads();
         const int limit = s_front > INT_MAX - PJ_FRONT ? INT_MAX : s_front + PJ_FRONT;
         /* A. stamps */
-        for (int q = myFirst; q < nq && q < limit; q += NT) {
+        for (int q = myFirst; q < nq && q < limit; q += NG) {
             if (status[q * 7] != PJ_PENDING) continue;
             const orbfe_proj_query p = qs[q];
-            if (p.flags & (ORBFE_PQ_AFTER_LEFT | ORBFE_PQ_NEEDS_LEFT_WINDOW))
+            if ((p.flags & (ORBFE_PQ_AFTER_LEFT | ORBFE_PQ_NEEDS_LEFT_WINDOW)) && gl == 0)
                 res[q].accepted = (q > 0 && status[(q - 1) * 7] == PJ_PENDING) ? 0 : 1;   /* may I look at q-1 in step B? */
             if (!(p.flags & ORBFE_PQ_BLOCKS)) continue;   /* a map point without observations occupies nothing: no stamps */
             /* what a query takes is its best candidate, and that has to be within thHigh: only those rows (and their partners) get its
              * stamp.  With stamps on the whole window, queries whose windows overlap resolved one per round whether or not they competed. */
             const uint4 sa = __ldg(qdesc + 2 * q), sb = __ldg(qdesc + 2 * q + 1);
-            pj_window<CACHE>(fr, s, p, [&](int row, int oct, int j) {
+            pj_window<CACHE>(fr, s, p, gl, G, [&](int row, int oct, int j) {
                 if (PJ_TAKEN_FOR(s, row, q)) return;
                 if (pj_gated<CACHE>(fr, s, p, row, j, oct, gateRight)) return;
                 if (pj_ham(sa, sb, PJ_DESC_A(row, j), PJ_DESC_B(row, j)) > thHigh) return;
@@ -317,34 +349,60 @@ __global__ void __launch_bounds__(NT, MINB) k_search_by_projection(int maxKp, co
             });
         }
         __syncthreads();
-        /* B. scan, decide */
+        /* B. scan, decide.  The reference's update rule (`d < bestDist`: the old best becomes the second; `else if d < bestDist2`) keeps
+         * the two smallest candidates in the order (distance, position in the walk), so a lane keeps two keys distance << 16 | position
+         * and the lanes of a group merge theirs. */
         int pending = 0;
-        for (int q = myFirst; q < nq; q += NT) {
-            if (q >= limit) { pending++; break; }   /* behind the front: waits */
+        for (int q = myFirst; q < nq; q += NG) {
+            if (q >= limit) { pending += gl == 0; break; }   /* behind the front: waits */
             if (status[q * 7] != PJ_PENDING) continue;
             const orbfe_proj_query p = qs[q];
             if (p.flags & (ORBFE_PQ_AFTER_LEFT | ORBFE_PQ_NEEDS_LEFT_WINDOW)) {
-                if (res[q].accepted == 0) { pending++; continue; }
-                res[q].accepted = 0;
+                int may = gl == 0 ? res[q].accepted : 0;
+                may = __shfl_sync(gmask, may, leader);
+                if (may == 0) { pending += gl == 0; continue; }
+                if (gl == 0) res[q].accepted = 0;
                 const int prev = q > 0 && !(qs[q - 1].flags & ORBFE_PQ_RIGHT) ? status[(q - 1) * 7] : -2;
                 if (((p.flags & ORBFE_PQ_AFTER_LEFT) && prev == ORBFE_PS_RATIO_REJECTED) ||        /* `continue` at ORBmatcher.cc:117-118 */
                     ((p.flags & ORBFE_PQ_NEEDS_LEFT_WINDOW) && prev == ORBFE_PS_EMPTY_WINDOW)) {   /* `continue` at ORBmatcher.cc:2262-2263 */
-                    status[q * 7] = ORBFE_PS_DROPPED;
+                    __syncwarp(gmask);                   /* everyone of the group has read the status of q before it changes */
+                    if (gl == 0) status[q * 7] = ORBFE_PS_DROPPED;
                     continue;
                 }
             }
             const uint4 qa = __ldg(qdesc + 2 * q), qb = __ldg(qdesc + 2 * q + 1);
-            int bestDist = 256, bestLevel = -1, bestDist2 = 256, bestLevel2 = -1, bestIdx = -1, seen = 0;
+            unsigned k1 = 0xFFFFFFFFu, k2 = 0xFFFFFFFFu;
+            int seen = 0;
             int foreign = 257;   /* the closest candidate that carries the stamp of an earlier unresolved query */
-            pj_window<CACHE>(fr, s, p, [&](int row, int oct, int j) {
-                seen++;
+            pj_window<CACHE>(fr, s, p, gl, G, [&](int row, int oct, int j) {
+                seen = 1;
                 if (PJ_TAKEN_FOR(s, row, q)) return;
                 if (pj_gated<CACHE>(fr, s, p, row, j, oct, gateRight)) return;
                 const int dist = pj_ham(qa, qb, PJ_DESC_A(row, j), PJ_DESC_B(row, j));
-                if (dist < bestDist) { bestDist2 = bestDist; bestDist = dist; bestLevel2 = bestLevel; bestLevel = oct; bestIdx = row; }
-                else if (dist < bestDist2) { bestLevel2 = oct; bestDist2 = dist; }
+                const unsigned key = ((unsigned)dist << 16) | (unsigned)j;
+                if (key < k1) { k2 = k1; k1 = key; }
+                else if (key < k2) k2 = key;
                 if (s.owner[row] < q) foreign = min(foreign, dist);
             });
+            for (int o = G >> 1; o; o >>= 1) {
+                const unsigned o1 = __shfl_xor_sync(gmask, k1, o), o2 = __shfl_xor_sync(gmask, k2, o);
+                const unsigned lo = min(k1, o1), hi = max(k1, o1);
+                k2 = min(hi, min(k2, o2));
+                k1 = lo;
+                foreign = min(foreign, __shfl_xor_sync(gmask, foreign, o));
+                seen |= __shfl_xor_sync(gmask, seen, o);
+            }
+            int bestDist = 256, bestLevel = -1, bestDist2 = 256, bestLevel2 = -1, bestIdx = -1;
+            if (k1 != 0xFFFFFFFFu) {
+                const int j1 = (int)(k1 & 0xFFFFu);
+                bestDist = (int)(k1 >> 16); bestIdx = s.sorted[j1];
+                bestLevel = CACHE ? s.octS[j1] : __ldg(&fr.kps[bestIdx].octave);
+            }
+            if (k2 != 0xFFFFFFFFu) {
+                const int j2 = (int)(k2 & 0xFFFFu);
+                bestDist2 = (int)(k2 >> 16);
+                bestLevel2 = CACHE ? s.octS[j2] : __ldg(&fr.kps[s.sorted[j2]].octave);
+            }
             int st = seen ? ORBFE_PS_NO_CANDIDATES : ORBFE_PS_EMPTY_WINDOW;
             bool blocked = false;
             int partnerRow = -1;
@@ -358,14 +416,17 @@ __global__ void __launch_bounds__(NT, MINB) k_search_by_projection(int maxKp, co
                     if (pt >= 0 && pt < fr.n) { partnerRow = pt; if (s.owner[pt] < q) blocked = true; }
                 }
             }
-            if (blocked) { pending++; continue; }
-            orbfe_proj_match m;
-            m.best_idx = bestIdx; m.best_dist = bestDist; m.best_level = bestLevel; m.second_dist = bestDist2; m.second_level = bestLevel2;
-            m.accepted = st == ORBFE_PS_ACCEPTED ? 1 : 0; m.status = st;
-            res[q] = m;
-            if (st == ORBFE_PS_ACCEPTED && (p.flags & ORBFE_PQ_BLOCKS)) {
-                pj_take(s, bestIdx, q);
-                if (partnerRow >= 0) pj_take(s, partnerRow, q);
+            if (blocked) { pending += gl == 0; continue; }
+            __syncwarp(gmask);                           /* everyone of the group has read the status of q before it changes */
+            if (gl == 0) {
+                orbfe_proj_match m;
+                m.best_idx = bestIdx; m.best_dist = bestDist; m.best_level = bestLevel; m.second_dist = bestDist2; m.second_level = bestLevel2;
+                m.accepted = st == ORBFE_PS_ACCEPTED ? 1 : 0; m.status = st;
+                res[q] = m;
+                if (st == ORBFE_PS_ACCEPTED && (p.flags & ORBFE_PQ_BLOCKS)) {
+                    pj_take(s, bestIdx, q);
+                    if (partnerRow >= 0) pj_take(s, partnerRow, q);
+                }
             }
         }
         rounds++;
