@@ -648,31 +648,45 @@ int orbfe_bow_result(orbfe_vocabulary* v, int frame, int nfeatures, int32_t* wor
     if (!v || frame < 0 || frame >= v->maxBatch || nfeatures < 0 || nfeatures > v->maxFeatures) { orbfe_set_error("bad argument"); return ORBFE_E_INVALID; }
     ORBFE_CUDA(cudaSetDevice(v->device));
     ORBFE_CUDA(cudaEventSynchronize(v->evLast));
+    /* everything the frame produced in one round trip: the arrays are copied at the sizes known beforehand (nfeatures, and max_features for
+     * the vectors, a few tens of KB) into the calling thread's pinned block, one synchronisation, and the parts in use are handed out */
+    const size_t F = (size_t)v->maxFeatures, fo = (size_t)frame * F, so = (size_t)frame * (F + 1);
+    size_t off = 0;
+    auto take = [&](size_t bytes) { const size_t o = off; off += (bytes + 255) & ~(size_t)255; return o; };
+    const size_t oCnt = take(8), oWid = take((size_t)nfeatures * 4), oNid = take((size_t)nfeatures * 4), oBw = take(F * 4), oBv = take(F * 8);
+    const size_t oFn = take(F * 4), oFs = take((F + 1) * 4), oFf = take(F * 4);
+    OrbfeStaging ws;
+    const int rc = orbfe_thread_staging(v->device, off, &ws);
+    if (rc != ORBFE_OK) return rc;
+    uint8_t* h = ws.h;
 #define BOW_D2H(dst, src, bytes) ORBFE_CUDA(cudaMemcpyAsync((dst), (src), (bytes), cudaMemcpyDeviceToHost, v->stream))
-    const size_t fo = (size_t)frame * v->maxFeatures, so = (size_t)frame * (v->maxFeatures + 1);
-    int nb = 0, nn = 0;
-    BOW_D2H(&nb, v->bowCount + frame, 4);
-    BOW_D2H(&nn, v->fvCount + frame, 4);
+    BOW_D2H(h + oCnt, v->bowCount + frame, 4);
+    BOW_D2H(h + oCnt + 4, v->fvCount + frame, 4);
+    if (word_ids && nfeatures) BOW_D2H(h + oWid, v->featWord + fo, (size_t)nfeatures * 4);
+    if (node_ids && nfeatures) BOW_D2H(h + oNid, v->featNode + fo, (size_t)nfeatures * 4);
+    if (bow_words) BOW_D2H(h + oBw, v->bowWords + fo, F * 4);
+    if (bow_values) BOW_D2H(h + oBv, v->bowValues + fo, F * 8);
+    if (fv_nodes) BOW_D2H(h + oFn, v->fvNodes + fo, F * 4);
+    if (fv_starts || fv_feats) BOW_D2H(h + oFs, v->fvStarts + so, (F + 1) * 4);
+    if (fv_feats) BOW_D2H(h + oFf, v->fvFeats + fo, F * 4);
     ORBFE_CUDA(cudaStreamSynchronize(v->stream));
+    const int nb = ((const int32_t*)(h + oCnt))[0], nn = ((const int32_t*)(h + oCnt))[1];
     if (nb < 0 || nn < 0) {
         orbfe_set_error("frame %d of the batch has more than max_features = %d descriptors: its BoW vectors were not computed", frame, v->maxFeatures);
         return ORBFE_E_CAPACITY;
     }
     if (nbow) *nbow = nb;
     if (nfv) *nfv = nn;
-    if (word_ids && nfeatures) BOW_D2H(word_ids, v->featWord + fo, (size_t)nfeatures * 4);
-    if (node_ids && nfeatures) BOW_D2H(node_ids, v->featNode + fo, (size_t)nfeatures * 4);
-    if (bow_words && nb) BOW_D2H(bow_words, v->bowWords + fo, (size_t)nb * 4);
-    if (bow_values && nb) BOW_D2H(bow_values, v->bowValues + fo, (size_t)nb * 8);
-    if (fv_nodes && nn) BOW_D2H(fv_nodes, v->fvNodes + fo, (size_t)nn * 4);
-    if (fv_starts) BOW_D2H(fv_starts, v->fvStarts + so, (size_t)(nn + 1) * 4);
+    if (word_ids && nfeatures) memcpy(word_ids, h + oWid, (size_t)nfeatures * 4);
+    if (node_ids && nfeatures) memcpy(node_ids, h + oNid, (size_t)nfeatures * 4);
+    if (bow_words && nb) memcpy(bow_words, h + oBw, (size_t)nb * 4);
+    if (bow_values && nb) memcpy(bow_values, h + oBv, (size_t)nb * 8);
+    if (fv_nodes && nn) memcpy(fv_nodes, h + oFn, (size_t)nn * 4);
+    if (fv_starts) memcpy(fv_starts, h + oFs, (size_t)(nn + 1) * 4);
     if (fv_feats && nn) {
-        int total = 0;
-        BOW_D2H(&total, v->fvStarts + so + nn, 4);
-        ORBFE_CUDA(cudaStreamSynchronize(v->stream));
-        if (total) BOW_D2H(fv_feats, v->fvFeats + fo, (size_t)total * 4);
+        const int total = ((const int32_t*)(h + oFs))[nn];
+        if (total > 0) memcpy(fv_feats, h + oFf, (size_t)std::min<size_t>((size_t)total, F) * 4);
     }
-    ORBFE_CUDA(cudaStreamSynchronize(v->stream));
 #undef BOW_D2H
     return ORBFE_OK;
 }
