@@ -816,11 +816,11 @@ int orbfe_search_for_triangulation_device(int device, int npairs, int max_featur
     if (npairs > 65535) { orbfe_set_error("at most 65535 keyframe pairs per call"); return ORBFE_E_CAPACITY; }
     ORBFE_CUDA(cudaSetDevice(device));
     static_assert(sizeof(TriRig) == sizeof(orbfe_triangulation_rig), "rig layout");
-    /* matching over (split, pair) CTAs — a pair's nodes are dealt out over `split` CTAs, enough of them to cover the SMs twice when there are
-     * few pairs — then the rotation check, one CTA per pair */
+    /* matching over (split, pair) CTAs — a pair's nodes are dealt out over `split` CTAs, enough of them to fill the SMs — then the rotation
+     * check, one CTA per pair */
     int sms = 0;
     ORBFE_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
-    const int split = std::min(std::max((2 * sms + npairs - 1) / npairs, 1), 16);
+    const int split = std::min(std::max((5 * sms + npairs - 1) / npairs, 1), 16);   /* five 256-thread CTAs fit an SM (44 registers) */
     const dim3 grid(split, npairs);
     ORBFE_CUDA(cudaMemsetAsync(d_match_12, 0xFF, (size_t)npairs * row_stride * sizeof(int32_t), (cudaStream_t)stream));
     if (d_rigs)
