@@ -1195,6 +1195,17 @@ def main():
                 ("search_for_initialization", lambda: PJ.search_for_initialization(*[a.copy() if hasattr(a, "copy") else a for a in i0[:6]], 100, 0.9, True),
                  lambda: init_fn(*[a.copy() if hasattr(a, "copy") else a for a in i0[:6]], 100, 0.9, True))):
             one_call[name] = {"gpu_host_call_ms": med_ms(gpu_fn, 20), "cpu_one_thread_ms": med_ms(cpu_fn, 3) if cpu_fn else None}
+        # the loops the reference runs over independent pairs, as ONE call: CreateNewMapPoints' 20 neighbours, Relocalization's candidates
+        hframes = [dict(desc=bsample[i], kps=ksample[i], feat_vec=fvs[i]) for i in range(8)]
+        nb20 = [1 + (i % 7) for i in range(20)]
+        F20, ep20 = np.tile(F12.reshape(1, 9), (20, 1)).astype(np.float32), np.tile(np.array([[-3000.0, 240.0]], np.float32), (20, 1))
+        one_call["search_for_triangulation_20_neighbours"] = {
+            "gpu_host_call_ms": med_ms(lambda: BW.search_for_triangulation_frames(hframes, [0] * 20, nb20, F20, ep20, scale8, scale8 * scale8, 50, False, False, True), 20),
+            "cpu_one_thread_ms": med_ms(lambda: [O.search_for_triangulation(bsample[0], ksample[0], None, None, fvs[0], bsample[j], ksample[j], None, None, fvs[j], F12,
+                                                                            [-3000.0, 240.0], scale8, scale8 * scale8, 50, False, False, True) for j in nb20], 3)}
+        one_call["search_by_bow_20_candidates"] = {
+            "gpu_host_call_ms": med_ms(lambda: BW.search_by_bow_frames(hframes, nb20, [0] * 20, 50, 0.7, True), 20),
+            "cpu_one_thread_ms": med_ms(lambda: [O.search_by_bow(bsample[j], ksample[j], fvs[j], None, bsample[0], ksample[0], fvs[0], 50, 0.7, True) for j in nb20], 3)}
         cpu["one_call_latency"] = one_call
         cpu["one_call_latency_note"] = ("median wall time of ONE call of the host entry point a shim makes (host arrays in, host arrays out, copies included, Python "
                                         "ctypes glue on both sides) beside the CPU oracle / reference on one thread with the same inputs; extract = one 752x480 "

@@ -393,6 +393,36 @@ int orbfe_search_for_triangulation(int device, const uint8_t* desc_1, const orbf
                                    const float* scale_factors, const float* level_sigma2, int nlevels, int th_low, int only_stereo, int coarse,
                                    int check_orientation, int32_t* match_12, int* nmatches, const orbfe_triangulation_rig* rig);
 
+/* Many pairs over host memory in ONE call.  The reference calls these matchers in loops whose iterations do not depend on each other:
+ * LocalMapping::CreateNewMapPoints runs SearchForTriangulation of the current keyframe against each of its 10-20 neighbours
+ * (src/LocalMapping.cc:556-621), Tracking::Relocalization and LoopClosing run SearchByBoW against every candidate keyframe
+ * (src/Tracking.cc:3784, src/LoopClosing.cc:725).  One pair is too little work for a GPU (a call costs about what one CPU thread needs);
+ * the loop as one call costs little more than one pair.  frames[] lists every frame or keyframe once, the pairs index into it. */
+typedef struct orbfe_host_frame {
+    const uint8_t* desc;            /* n x 32 */
+    const orbfe_keypoint* kps;      /* n; may be NULL for SearchByBoW without check_orientation */
+    const float* u_right;           /* n, or NULL: no stereo keypoints */
+    const uint8_t* has_map_point;   /* n, or NULL: every row has one (SearchByBoW) / no row has one (SearchForTriangulation) */
+    int32_t n;
+    const int32_t* fv_nodes;        /* the FeatureVector: nfv node ids ascending, */
+    const int32_t* fv_starts;       /* nfv + 1 offsets into fv_feats, */
+    const int32_t* fv_feats;        /* feature rows, in the map's order */
+    int32_t nfv;
+    int32_t n_left;                 /* F.Nleft for the frame side of SearchByBoW; -1 without a second camera */
+} orbfe_host_frame;
+/* orbfe_search_for_triangulation for pairs (frames[pair_1[p]], frames[pair_2[p]]), p < npairs: f12 = 9 floats and epipole = 2 floats per pair, rigs =
+ * one orbfe_triangulation_rig per pair or NULL.  match_12[p * match_stride + i] = vMatches12[i] of pair p (match_stride >= the n of every first
+ * keyframe), nmatches[p] = its return value. */
+int orbfe_search_for_triangulation_frames(int device, const orbfe_host_frame* frames, int nframes, const int32_t* pair_1, const int32_t* pair_2, int npairs,
+                                          const float* f12, const float* epipole, const float* scale_factors, const float* level_sigma2, int nlevels, int th_low,
+                                          int only_stereo, int coarse, int check_orientation, int32_t* match_12, int match_stride, int32_t* nmatches,
+                                          const orbfe_triangulation_rig* rigs);
+/* orbfe_search_by_bow for pairs (keyframe frames[pair_kf[p]], frame frames[pair_f[p]]): match_f[p * match_stride + i] = the keyframe row matched to
+ * row i of the frame or -1 (match_stride >= the n of every frame side), kf_out (may be NULL) = npairs x match_stride records as in
+ * orbfe_search_by_bow (match_stride >= the n of every keyframe side too when it is asked for), nmatches[p] = the return value. */
+int orbfe_search_by_bow_frames(int device, const orbfe_host_frame* frames, int nframes, const int32_t* pair_kf, const int32_t* pair_f, int npairs, int th_low,
+                               float nnratio, int check_orientation, int kf_kf, int32_t* match_f, int match_stride, orbfe_match* kf_out, int32_t* nmatches);
+
 /* Replaces the computation of MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:349-423) for many map points at once
  * (SURVEY.md §8f N4): map point p owns the descriptor rows [offsets[p], offsets[p+1]) (the rows of vDescriptors, :352-384);
  * best_idx[p] = BestIdx, the row (relative to offsets[p]) with the least median distance to all rows of the point,

@@ -98,6 +98,8 @@ SIGNATURES = {
     "orbfe_search_by_bow_device": (i32, [i32, i32, i32, vp, vp, vp, vp, i32, vp, vp, vp, vp, vp, vp, i32, C.c_float, i32, i32, vp, vp, vp, vp]),
     "orbfe_search_by_bow": (i32, [i32, vp, vp, i32, vp, vp, vp, i32, vp, vp, vp, i32, vp, vp, vp, i32, vp, i32, i32, C.c_float, i32, i32, vp, vp, C.POINTER(i32)]),
     "orbfe_search_for_triangulation_device": (i32, [i32, i32, i32, vp, vp, vp, vp, vp, i32, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, vp, vp, vp, vp]),
+    "orbfe_search_for_triangulation_frames": (i32, [i32, vp, i32, vp, vp, i32, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp, i32, vp, vp]),
+    "orbfe_search_by_bow_frames": (i32, [i32, vp, i32, vp, vp, i32, i32, C.c_float, i32, i32, vp, i32, vp, vp]),
     "orbfe_search_for_triangulation": (i32, [i32, vp, vp, vp, vp, i32, vp, vp, vp, i32, vp, vp, vp, vp, i32, vp, vp, vp, i32, vp, vp, vp, vp, i32, i32, i32, i32,
                                              i32, vp, C.POINTER(i32), vp]),
     "orbfe_distinctive_descriptors_device": (i32, [i32, vp, vp, i32, vp, vp, vp]),

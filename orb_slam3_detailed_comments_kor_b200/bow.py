@@ -124,3 +124,57 @@ def search_for_triangulation(desc_1, kps_1, u_right_1, has_mp_1, fv_1, desc_2, k
                                                     d2.shape[0], p(n2), p(s2), p(f2), len(n2), p(F), p(ep), p(sf), p(ls), len(sf), th_low, int(only_stereo),
                                                     int(coarse), int(check_orientation), p(out), C.byref(nm), p(rig)))
     return out[:d1.shape[0]], nm.value
+
+
+class _HostFrame(C.Structure):
+    """orbfe_host_frame"""
+    _fields_ = [("desc", C.c_void_p), ("kps", C.c_void_p), ("u_right", C.c_void_p), ("has_map_point", C.c_void_p), ("n", C.c_int32),
+                ("fv_nodes", C.c_void_p), ("fv_starts", C.c_void_p), ("fv_feats", C.c_void_p), ("nfv", C.c_int32), ("n_left", C.c_int32)]
+
+
+def _host_frames(frames):
+    """frames: dicts with desc [n, 32], kps, feat_vec and optionally u_right, has_map_point, n_left.  Returns (ctypes array, the numpy arrays it
+    points into, which must outlive the call)."""
+    arr = (_HostFrame * len(frames))()
+    keep = []
+    for i, f in enumerate(frames):
+        c = lambda a, t: None if a is None else np.ascontiguousarray(a, t)  # noqa: E731
+        d, k = c(f["desc"], np.uint8), c(f.get("kps"), KP_DTYPE)
+        u, m = c(f.get("u_right"), np.float32), c(f.get("has_map_point"), np.uint8)
+        n, s, ff = _fv_arrays(f["feat_vec"])
+        keep += [d, k, u, m, n, s, ff]
+        a = lambda x: x.ctypes.data if x is not None and x.size else None  # noqa: E731
+        arr[i] = _HostFrame(a(d), a(k), a(u), a(m), d.shape[0], a(n), s.ctypes.data if len(n) else None, a(ff), len(n), int(f.get("n_left", -1)))
+    return arr, keep
+
+
+def search_for_triangulation_frames(frames, pair_1, pair_2, f12, epipole, scale_factors, level_sigma2, th_low=50, only_stereo=False, coarse=False,
+                                    check_orientation=True, rigs=None, device=0):
+    """orbfe_search_for_triangulation_frames: SearchForTriangulation for many keyframe pairs in one call (LocalMapping::CreateNewMapPoints' loop over
+    the neighbours).  f12: [npairs, 9], epipole: [npairs, 2], rigs: list of make_triangulation_rig() byte arrays or None.  Returns (list of
+    vMatches12 arrays, nmatches[npairs])."""
+    arr, keep = _host_frames(frames)
+    p1, p2 = np.ascontiguousarray(pair_1, np.int32), np.ascontiguousarray(pair_2, np.int32)
+    F, ep = np.ascontiguousarray(f12, np.float32).reshape(len(p1), 9), np.ascontiguousarray(epipole, np.float32).reshape(len(p1), 2)
+    sf, ls = np.ascontiguousarray(scale_factors, np.float32), np.ascontiguousarray(level_sigma2, np.float32)
+    stride = max(max(f["desc"].shape[0] for f in frames), 1)
+    out, nm = np.zeros((len(p1), stride), np.int32), np.zeros(len(p1), np.int32)
+    rg = None if rigs is None else np.ascontiguousarray(np.concatenate([np.asarray(r, np.uint8) for r in rigs]))
+    check(_lib.lib().orbfe_search_for_triangulation_frames(device, C.addressof(arr), len(frames), ptr(p1), ptr(p2), len(p1), ptr(F), ptr(ep), ptr(sf), ptr(ls), len(sf),
+                                                           th_low, int(only_stereo), int(coarse), int(check_orientation), ptr(out), stride, ptr(nm),
+                                                           ptr(rg) if rg is not None else None))
+    return [out[p, :frames[int(p1[p])]["desc"].shape[0]] for p in range(len(p1))], nm
+
+
+def search_by_bow_frames(frames, pair_kf, pair_f, th_low=50, nnratio=0.7, check_orientation=True, kf_kf=False, want_kf_out=False, device=0):
+    """orbfe_search_by_bow_frames: SearchByBoW for many (keyframe, frame) pairs in one call (the candidate loops of Tracking::Relocalization and
+    LoopClosing).  Returns (list of per-frame-row match arrays, list of kf_out arrays or None, nmatches[npairs])."""
+    arr, keep = _host_frames(frames)
+    pk, pf = np.ascontiguousarray(pair_kf, np.int32), np.ascontiguousarray(pair_f, np.int32)
+    stride = max(max(f["desc"].shape[0] for f in frames), 1)
+    out, nm = np.zeros((len(pk), stride), np.int32), np.zeros(len(pk), np.int32)
+    ko = np.zeros((len(pk), stride), MATCH_DTYPE) if want_kf_out else None
+    check(_lib.lib().orbfe_search_by_bow_frames(device, C.addressof(arr), len(frames), ptr(pk), ptr(pf), len(pk), th_low, C.c_float(nnratio), int(check_orientation),
+                                                int(kf_kf), ptr(out), stride, ptr(ko) if ko is not None else None, ptr(nm)))
+    n = lambda i: frames[int(i)]["desc"].shape[0]  # noqa: E731
+    return [out[p, :n(pf[p])] for p in range(len(pk))], ([ko[p, :n(pk[p])] for p in range(len(pk))] if want_kf_out else None), nm

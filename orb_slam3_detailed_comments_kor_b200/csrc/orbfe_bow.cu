@@ -904,4 +904,164 @@ int orbfe_search_for_triangulation(int device, const uint8_t* desc_1, const orbf
     return ORBFE_OK;
 }
 
+/* ---- many pairs over host memory: the frames packed once into the strided layout of the batch entry points, in the thread's staging block ---- */
+struct FramesPack {
+    int S;                                            /* rows per frame in the strided layout (the largest n, at least 1) */
+    size_t oDesc, oKps, oUr, oMp, oNodes, oStarts, oFeats, oCount, oLeft, end;
+};
+
+static size_t frames_max_rows(const orbfe_host_frame* frames, int nframes) {
+    int S = 1;
+    for (int f = 0; frames && f < nframes; f++) S = std::max(S, std::min(frames[f].n, BOW_MAXF));
+    return (size_t)S;
+}
+
+/* validates the frames and the pair lists, lays the block out from offset 0 and fills its host side; mpDefault = what a NULL has_map_point means */
+static int frames_pack(const orbfe_host_frame* frames, int nframes, const int32_t* pa, const int32_t* pb, int npairs, bool needKps, uint8_t mpDefault,
+                       FramesPack* fp, size_t extraBytes, int device, OrbfeStaging* ws, size_t* extraOff) {
+    if (!frames || nframes < 1 || !pa || !pb || npairs < 1) { orbfe_set_error("bad argument"); return ORBFE_E_INVALID; }
+    int S = 1;
+    for (int f = 0; f < nframes; f++) {
+        const orbfe_host_frame& fr = frames[f];
+        if (fr.n < 0 || fr.nfv < 0 || (fr.n && (!fr.desc || (needKps && !fr.kps))) || (fr.nfv && (!fr.fv_nodes || !fr.fv_starts || !fr.fv_feats))) {
+            orbfe_set_error("frame %d: bad argument", f);
+            return ORBFE_E_INVALID;
+        }
+        if (fr.n > BOW_MAXF) { orbfe_set_error("at most %d features per frame", BOW_MAXF); return ORBFE_E_CAPACITY; }
+        if (fr.nfv > std::max(fr.n, 1) || (fr.nfv && (fr.fv_starts[fr.nfv] > fr.n || fr.fv_starts[fr.nfv] < 0))) {
+            orbfe_set_error("frame %d: feature vector longer than the frame", f);
+            return ORBFE_E_INVALID;
+        }
+        S = std::max(S, fr.n);
+    }
+    for (int p = 0; p < npairs; p++)
+        if (pa[p] < 0 || pa[p] >= nframes || pb[p] < 0 || pb[p] >= nframes) { orbfe_set_error("pair %d names a frame outside the list", p); return ORBFE_E_INVALID; }
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev) {
+        orbfe_set_error("no usable CUDA device %d (found %d); this library has no CPU path", device, ndev);
+        return ORBFE_E_CUDA;
+    }
+    size_t off = 0;
+    auto take = [&](size_t bytes) { const size_t o = off; off += (bytes + 255) & ~(size_t)255; return o; };
+    const size_t N = (size_t)nframes;
+    fp->S = S;
+    fp->oDesc = take(N * S * 32); fp->oKps = take(N * S * sizeof(orbfe_keypoint)); fp->oUr = take(N * S * 4); fp->oMp = take(N * S);
+    fp->oNodes = take(N * S * 4); fp->oStarts = take(N * (S + 1) * 4); fp->oFeats = take(N * S * 4); fp->oCount = take(N * 4); fp->oLeft = take(N * 4);
+    fp->end = off;
+    *extraOff = off;
+    if (off + extraBytes > ((size_t)1 << 30)) { orbfe_set_error("the frames of one call must fit 1 GB"); return ORBFE_E_CAPACITY; }
+    const int rc = orbfe_thread_staging(device, off + extraBytes, ws);
+    if (rc != ORBFE_OK) return rc;
+    uint8_t* h = ws->h;
+    for (int f = 0; f < nframes; f++) {
+        const orbfe_host_frame& fr = frames[f];
+        const size_t r0 = (size_t)f * S;
+        if (fr.n) {
+            memcpy(h + fp->oDesc + r0 * 32, fr.desc, (size_t)fr.n * 32);
+            if (fr.kps) memcpy(h + fp->oKps + r0 * sizeof(orbfe_keypoint), fr.kps, (size_t)fr.n * sizeof(orbfe_keypoint));
+            else memset(h + fp->oKps + r0 * sizeof(orbfe_keypoint), 0, (size_t)fr.n * sizeof(orbfe_keypoint));
+            float* ur = (float*)(h + fp->oUr) + r0;
+            if (fr.u_right) memcpy(ur, fr.u_right, (size_t)fr.n * 4);
+            else for (int i = 0; i < fr.n; i++) ur[i] = -1.0f;
+            if (fr.has_map_point) memcpy(h + fp->oMp + r0, fr.has_map_point, (size_t)fr.n);
+            else memset(h + fp->oMp + r0, mpDefault, (size_t)fr.n);
+        }
+        if (fr.nfv) {
+            memcpy((int32_t*)(h + fp->oNodes) + r0, fr.fv_nodes, (size_t)fr.nfv * 4);
+            memcpy((int32_t*)(h + fp->oStarts) + (size_t)f * (S + 1), fr.fv_starts, (size_t)(fr.nfv + 1) * 4);
+            memcpy((int32_t*)(h + fp->oFeats) + r0, fr.fv_feats, (size_t)fr.fv_starts[fr.nfv] * 4);
+        }
+        ((int32_t*)(h + fp->oCount))[f] = fr.nfv;
+        ((int32_t*)(h + fp->oLeft))[f] = fr.n_left < 0 ? -1 : fr.n_left;
+    }
+    return ORBFE_OK;
+}
+
+int orbfe_search_for_triangulation_frames(int device, const orbfe_host_frame* frames, int nframes, const int32_t* pair_1, const int32_t* pair_2, int npairs,
+                                          const float* f12, const float* epipole, const float* scale_factors, const float* level_sigma2, int nlevels, int th_low,
+                                          int only_stereo, int coarse, int check_orientation, int32_t* match_12, int match_stride, int32_t* nmatches,
+                                          const orbfe_triangulation_rig* rigs) {
+    if (!f12 || !epipole || !scale_factors || !level_sigma2 || nlevels < 1 || nlevels > 16 || !match_12 || match_stride < 1) { orbfe_set_error("bad argument"); return ORBFE_E_INVALID; }
+    FramesPack fp;
+    OrbfeStaging ws;
+    size_t x = 0;
+    /* behind the frames: pair lists, F12, epipoles, the two level tables, the rigs | outputs: matches, counts */
+    const size_t P = (size_t)(npairs > 0 ? npairs : 0);
+    auto up = [](size_t b) { return (b + 255) & ~(size_t)255; };
+    const size_t bPairs = up(P * 8), bF = up(P * 36), bE = up(P * 8), bLv = up(32 * 4), bRig = up(P * sizeof(orbfe_triangulation_rig));
+    int rc = frames_pack(frames, nframes, pair_1, pair_2, npairs, true, 0, &fp, bPairs + bF + bE + bLv + bRig + up(P * frames_max_rows(frames, nframes) * 4) + up(P * 4), device, &ws, &x);
+    if (rc != ORBFE_OK) return rc;
+    for (int p = 0; p < npairs; p++)
+        if (frames[pair_1[p]].n > match_stride) { orbfe_set_error("pair %d: match_stride %d below the keyframe's %d rows", p, match_stride, frames[pair_1[p]].n); return ORBFE_E_INVALID; }
+    const int S = fp.S;
+    const size_t oPairs = x, oF = oPairs + bPairs, oE = oF + bF, oLv = oE + bE, oRig = oLv + bLv, inEnd = oRig + bRig;
+    const size_t oMatch = inEnd, oNm = oMatch + up(P * S * 4), total = oNm + up(P * 4);
+    uint8_t* h = ws.h;
+    uint8_t* d = ws.d;
+    memcpy(h + oPairs, pair_1, P * 4); memcpy(h + oPairs + P * 4, pair_2, P * 4);
+    memcpy(h + oF, f12, P * 36); memcpy(h + oE, epipole, P * 8);
+    memset(h + oLv, 0, 32 * 4);
+    memcpy(h + oLv, scale_factors, (size_t)nlevels * 4); memcpy(h + oLv + 64, level_sigma2, (size_t)nlevels * 4);
+    if (rigs) memcpy(h + oRig, rigs, P * sizeof(orbfe_triangulation_rig));
+    cudaError_t e = cudaMemcpyAsync(d, h, inEnd, cudaMemcpyHostToDevice, ws.stream);
+    if (e == cudaSuccess)
+        rc = orbfe_search_for_triangulation_device(device, npairs, S, (const int32_t*)(d + oPairs), (const int32_t*)(d + oPairs) + P, d + fp.oDesc,
+                                                   (const orbfe_keypoint*)(d + fp.oKps), (const float*)(d + fp.oUr), S, (const int32_t*)(d + fp.oNodes),
+                                                   (const int32_t*)(d + fp.oStarts), (const int32_t*)(d + fp.oFeats), (const int32_t*)(d + fp.oCount), d + fp.oMp,
+                                                   (const float*)(d + oF), (const float*)(d + oE), (const float*)(d + oLv), (const float*)(d + oLv) + 16, th_low,
+                                                   only_stereo, coarse, check_orientation, (int32_t*)(d + oMatch), (int32_t*)(d + oNm), ws.stream,
+                                                   rigs ? (const orbfe_triangulation_rig*)(d + oRig) : nullptr);
+    if (rc == ORBFE_OK && e == cudaSuccess) e = cudaMemcpyAsync(h + oMatch, d + oMatch, total - oMatch, cudaMemcpyDeviceToHost, ws.stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ws.stream);
+    if (rc != ORBFE_OK) return rc;
+    if (e != cudaSuccess) return orbfe_cuda_fail(e, "search_for_triangulation_frames");
+    for (int p = 0; p < npairs; p++) {
+        const int n1 = frames[pair_1[p]].n;
+        if (n1) memcpy(match_12 + (size_t)p * match_stride, h + oMatch + (size_t)p * S * 4, (size_t)n1 * 4);
+        if (nmatches) nmatches[p] = ((const int32_t*)(h + oNm))[p];
+    }
+    return ORBFE_OK;
+}
+
+int orbfe_search_by_bow_frames(int device, const orbfe_host_frame* frames, int nframes, const int32_t* pair_kf, const int32_t* pair_f, int npairs, int th_low,
+                               float nnratio, int check_orientation, int kf_kf, int32_t* match_f, int match_stride, orbfe_match* kf_out, int32_t* nmatches) {
+    if (!match_f || match_stride < 1) { orbfe_set_error("bad argument"); return ORBFE_E_INVALID; }
+    FramesPack fp;
+    OrbfeStaging ws;
+    size_t x = 0;
+    const size_t P = (size_t)(npairs > 0 ? npairs : 0);
+    auto up = [](size_t b) { return (b + 255) & ~(size_t)255; };
+    const size_t bPairs = up(P * 8);
+    int rc = frames_pack(frames, nframes, pair_kf, pair_f, npairs, check_orientation != 0, 1, &fp,
+                         bPairs + up(P * frames_max_rows(frames, nframes) * 4) + up(P * frames_max_rows(frames, nframes) * sizeof(orbfe_match)) + up(P * 4), device, &ws, &x);
+    if (rc != ORBFE_OK) return rc;
+    for (int p = 0; p < npairs; p++)
+        if (frames[pair_f[p]].n > match_stride || (kf_out && frames[pair_kf[p]].n > match_stride)) {
+            orbfe_set_error("pair %d: match_stride %d below the rows of its frames", p, match_stride);
+            return ORBFE_E_INVALID;
+        }
+    const int S = fp.S;
+    const size_t oPairs = x, inEnd = oPairs + bPairs, oMatch = inEnd, oKf = oMatch + up(P * S * 4), oNm = oKf + up(P * S * sizeof(orbfe_match)), total = oNm + up(P * 4);
+    uint8_t* h = ws.h;
+    uint8_t* d = ws.d;
+    memcpy(h + oPairs, pair_kf, P * 4); memcpy(h + oPairs + P * 4, pair_f, P * 4);
+    cudaError_t e = cudaMemcpyAsync(d, h, inEnd, cudaMemcpyHostToDevice, ws.stream);
+    if (e == cudaSuccess)
+        rc = orbfe_search_by_bow_device(device, npairs, S, (const int32_t*)(d + oPairs), (const int32_t*)(d + oPairs) + P, d + fp.oDesc, (const orbfe_keypoint*)(d + fp.oKps), S,
+                                        (const int32_t*)(d + fp.oNodes), (const int32_t*)(d + fp.oStarts), (const int32_t*)(d + fp.oFeats), (const int32_t*)(d + fp.oCount),
+                                        d + fp.oMp, (const int32_t*)(d + fp.oLeft), th_low, nnratio, check_orientation, kf_kf, (int32_t*)(d + oMatch),
+                                        kf_out ? (orbfe_match*)(d + oKf) : nullptr, (int32_t*)(d + oNm), ws.stream);
+    if (rc == ORBFE_OK && e == cudaSuccess) e = cudaMemcpyAsync(h + oMatch, d + oMatch, total - oMatch, cudaMemcpyDeviceToHost, ws.stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ws.stream);
+    if (rc != ORBFE_OK) return rc;
+    if (e != cudaSuccess) return orbfe_cuda_fail(e, "search_by_bow_frames");
+    for (int p = 0; p < npairs; p++) {
+        const int nf = frames[pair_f[p]].n, nk = frames[pair_kf[p]].n;
+        if (nf) memcpy(match_f + (size_t)p * match_stride, h + oMatch + (size_t)p * S * 4, (size_t)nf * 4);
+        if (kf_out && nk) memcpy(kf_out + (size_t)p * match_stride, h + oKf + (size_t)p * S * sizeof(orbfe_match), (size_t)nk * sizeof(orbfe_match));
+        if (nmatches) nmatches[p] = ((const int32_t*)(h + oNm))[p];
+    }
+    return ORBFE_OK;
+}
+
 }  /* extern "C" */

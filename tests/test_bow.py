@@ -723,3 +723,51 @@ def test_gpu_search_for_triangulation_rig_matches_oracle():
             assert ndiff <= max(1, len(d1) // 500), (cfg, coarse, ori, ndiff)
             assert ndiff == 0 and got[1] == want[1], (cfg, coarse, ori, ndiff)
             assert want[1] > 20
+
+
+# ----------------------------------------------------------------------- many pairs over host memory in one call
+@pytest.mark.gpu
+def test_gpu_frames_entry_points_equal_the_oracle_pair_by_pair():
+    """orbfe_search_for_triangulation_frames / orbfe_search_by_bow_frames: the loops of CreateNewMapPoints, Relocalization and LoopClosing as one
+    call.  Frames of different sizes (one empty), a pair of a frame with itself, every pair checked against the oracle on that pair alone."""
+    from orb_slam3_detailed_comments_kor_b200 import bow as B
+    from orb_slam3_detailed_comments_kor_b200._lib import OrbfeError
+    k, L, levelsup, seed = 10, 3, 1, 71
+    rows = make_vocabulary(seed, k, L)
+    voc = O.OracleVocabulary(k, L, 0, 0, *rows)
+    # keyframes 0..4 share a scene (triangulation pairs against keyframe 0), 5 is empty
+    base = make_triangulation_pair(seed, rows, 900)
+    d1, k1, u1, mp1, d2, k2, u2, mp2, F, ep, scale, sigma2 = base
+    frames = [dict(desc=d1, kps=k1, u_right=u1, has_map_point=mp1, feat_vec=voc.transform(d1, levelsup)["feat_vec"])]
+    Fs, eps = [], []
+    rng = np.random.RandomState(seed)
+    for i, n in enumerate((900, 650, 1200, 300)):
+        keep = rng.permutation(len(d2))[:min(n, len(d2))]
+        dd, kk, uu, mm = d2[keep].copy(), k2[keep].copy(), u2[keep].copy(), mp2[keep].copy()
+        frames.append(dict(desc=dd, kps=kk, u_right=uu, has_map_point=mm, feat_vec=voc.transform(dd, levelsup)["feat_vec"]))
+        Fs.append((F * np.float32(1.0 + 0.01 * i)).astype(np.float32)); eps.append(ep)
+    frames.append(dict(desc=d1[:0], kps=k1[:0], u_right=u1[:0], has_map_point=mp1[:0], feat_vec={}))
+    p1, p2 = [0, 0, 0, 0, 0, 2], [1, 2, 3, 4, 5, 2]
+    Fs += [F, F]; eps += [ep, ep]
+    for only_stereo, coarse, ori in ((False, False, True), (False, True, False)):
+        got, nm = B.search_for_triangulation_frames(frames, p1, p2, np.stack(Fs), np.stack(eps), scale, sigma2, 50, only_stereo, coarse, ori)
+        for p, (a, b) in enumerate(zip(p1, p2)):
+            fa, fb = frames[a], frames[b]
+            want = O.search_for_triangulation(fa["desc"], fa["kps"], fa["u_right"], fa["has_map_point"], fa["feat_vec"], fb["desc"], fb["kps"], fb["u_right"],
+                                              fb["has_map_point"], fb["feat_vec"], Fs[p], eps[p], scale, sigma2, 50, only_stereo, coarse, ori)
+            assert np.array_equal(got[p], want[0]) and nm[p] == want[1], (p, a, b, only_stereo, coarse, ori)
+        assert nm[:4].min() > 20
+    # SearchByBoW: frame 0 (the current frame) against candidate keyframes, both overloads, with and without kf_out
+    for kf_kf in (False, True):
+        pk, pf = [1, 2, 3, 4, 5, 0], [0, 0, 0, 0, 0, 0]
+        got, ko, nm = B.search_by_bow_frames(frames, pk, pf, 50 if not kf_kf else 20, 0.7, True, kf_kf, want_kf_out=True)
+        got2, _, nm2 = B.search_by_bow_frames(frames, pk, pf, 50 if not kf_kf else 20, 0.7, True, kf_kf)
+        for p, (a, b) in enumerate(zip(pk, pf)):
+            fa, fb = frames[a], frames[b]
+            want = O.search_by_bow(fa["desc"], fa["kps"], fa["feat_vec"], fa["has_map_point"], fb["desc"], fb["kps"], fb["feat_vec"], 50 if not kf_kf else 20, 0.7,
+                                   True, kf_kf=kf_kf, has_map_point_f=fb["has_map_point"])
+            assert np.array_equal(got[p], want[0]) and nm[p] == want[2] and np.array_equal(ko[p], want[1]), (p, a, b, kf_kf)
+            assert np.array_equal(got2[p], want[0]) and nm2[p] == want[2]
+    assert nm.max() > 20
+    with pytest.raises(OrbfeError):
+        B.search_by_bow_frames(frames, [0, 9], [1, 1])
