@@ -13,6 +13,7 @@
 #define ORBFE_SHIM_MATCHING_H
 
 #include <algorithm>
+#include <cstdint>
 #include <cstring>
 #include <stdexcept>
 #include <string>
@@ -165,6 +166,83 @@ inline int SearchForInitialization(const std::vector<cv::KeyPoint>& keys1, const
                                         reinterpret_cast<float*>(vbPrevMatched.data()), windowSize, mfNNratio, checkOrientation ? 1 : 0, thLow,
                                         vnMatches12.data(), &nmatches) != ORBFE_OK)
         throw std::runtime_error(std::string("orbfe_search_for_initialization: ") + orbfe_last_error());
+    return nmatches;
+}
+
+/* DBoW2::FeatureVector (a std::map<NodeId, std::vector<unsigned int>>, Thirdparty/DBoW2/DBoW2/FeatureVector.h) — or any ordered map from node id to
+ * feature rows — as the three arrays the C ABI takes: node ids ascending, offsets, rows in the map's order. */
+template <class FeatureVector>
+inline void FlattenFeatureVector(const FeatureVector& fv, std::vector<int32_t>& nodes, std::vector<int32_t>& starts, std::vector<int32_t>& feats) {
+    nodes.clear(); feats.clear();
+    starts.assign(1, 0);
+    for (const auto& kv : fv) {
+        nodes.push_back((int32_t)kv.first);
+        for (const auto r : kv.second) feats.push_back((int32_t)r);
+        starts.push_back((int32_t)feats.size());
+    }
+}
+
+inline void PackDescriptors(const cv::Mat& descriptors, int n, std::vector<unsigned char>& out) {
+    out.resize((size_t)n * 32);
+    for (int i = 0; i < n; i++) std::memcpy(&out[(size_t)i * 32], descriptors.ptr<unsigned char>(i), 32);
+}
+
+/* The search of ORBmatcher::SearchByBoW(KeyFrame* pKF, Frame &F, vector<MapPoint*> &vpMapPointMatches) (src/ORBmatcher.cc:269-470): keysKF /
+ * descriptorsKF / fvKF = pKF->mvKeysUn, mDescriptors, mFeatVec; hasMapPointKF[r] = vpMapPointsKF[r] && !vpMapPointsKF[r]->isBad(); the frame
+ * likewise with F.mvKeys (followed by mvKeysRight on a fisheye rig, NleftF = F.Nleft).  matchF[i] = keyframe row whose map point row i of the
+ * frame receives, or -1; the return value is nmatches.  kfkf = the keyframe-keyframe overload (:823-963; thLow, hasMapPointF as there). */
+template <class FeatureVector>
+inline int SearchByBoW(const cv::Mat& descriptorsKF, const std::vector<cv::KeyPoint>& keysKF, const FeatureVector& fvKF, const std::vector<unsigned char>& hasMapPointKF,
+                       const cv::Mat& descriptorsF, const std::vector<cv::KeyPoint>& keysF, const FeatureVector& fvF, int NleftF, float mfNNratio,
+                       bool checkOrientation, std::vector<int>& matchF, int thLow = 50, bool kfkf = false, const std::vector<unsigned char>* hasMapPointF = nullptr,
+                       int device = 0) {
+    static_assert(sizeof(cv::KeyPoint) == sizeof(orbfe_keypoint), "cv::KeyPoint layout");
+    const int nk = (int)keysKF.size(), nf = (int)keysF.size();
+    std::vector<unsigned char> dk, df;
+    PackDescriptors(descriptorsKF, nk, dk);
+    PackDescriptors(descriptorsF, nf, df);
+    std::vector<int32_t> nA, sA, fA, nB, sB, fB;
+    FlattenFeatureVector(fvKF, nA, sA, fA);
+    FlattenFeatureVector(fvF, nB, sB, fB);
+    matchF.assign(nf > 0 ? nf : 1, -1);
+    int nmatches = 0;
+    if (orbfe_search_by_bow(device, dk.data(), reinterpret_cast<const orbfe_keypoint*>(keysKF.data()), nk, nA.data(), sA.data(), fA.data(), (int)nA.size(),
+                            hasMapPointKF.empty() ? nullptr : hasMapPointKF.data(), df.data(), reinterpret_cast<const orbfe_keypoint*>(keysF.data()), nf, nB.data(),
+                            sB.data(), fB.data(), (int)nB.size(), hasMapPointF && !hasMapPointF->empty() ? hasMapPointF->data() : nullptr, NleftF, thLow, mfNNratio,
+                            checkOrientation ? 1 : 0, kfkf ? 1 : 0, matchF.data(), nullptr, &nmatches) != ORBFE_OK)
+        throw std::runtime_error(std::string("orbfe_search_by_bow: ") + orbfe_last_error());
+    matchF.resize(nf);
+    return nmatches;
+}
+
+/* The search of ORBmatcher::SearchForTriangulation(pKF1, pKF2, F12, vMatchedPairs, bOnlyStereo, bCoarse) (src/ORBmatcher.cc:965-1206): F12 row-major
+ * (Pinhole.cpp:137-140), ep = pKF2->mpCamera->project(C2) (:974-977), scaleFactors / levelSigma2 = pKF2->mvScaleFactors / mvLevelSigma2,
+ * hasMapPoint1/2[r] = pKF->GetMapPoint(r) != NULL, uRight1/2 = mvuRight (NULL: monocular).  vMatches12[r] = row of keyframe 2 or -1; the
+ * caller builds vMatchedPairs from it (:1196-1203).  rig: the two-camera case (see orbfe.h), NULL for pinhole keyframes. */
+template <class FeatureVector>
+inline int SearchForTriangulation(const cv::Mat& descriptors1, const std::vector<cv::KeyPoint>& keys1, const std::vector<float>* uRight1,
+                                  const std::vector<unsigned char>& hasMapPoint1, const FeatureVector& fv1, const cv::Mat& descriptors2,
+                                  const std::vector<cv::KeyPoint>& keys2, const std::vector<float>* uRight2, const std::vector<unsigned char>& hasMapPoint2,
+                                  const FeatureVector& fv2, const float F12[9], const float ep[2], const std::vector<float>& scaleFactors,
+                                  const std::vector<float>& levelSigma2, bool bOnlyStereo, bool bCoarse, bool checkOrientation, std::vector<int>& vMatches12,
+                                  int thLow = 50, const orbfe_triangulation_rig* rig = nullptr, int device = 0) {
+    const int n1 = (int)keys1.size(), n2 = (int)keys2.size();
+    std::vector<unsigned char> d1, d2;
+    PackDescriptors(descriptors1, n1, d1);
+    PackDescriptors(descriptors2, n2, d2);
+    std::vector<int32_t> nA, sA, fA, nB, sB, fB;
+    FlattenFeatureVector(fv1, nA, sA, fA);
+    FlattenFeatureVector(fv2, nB, sB, fB);
+    vMatches12.assign(n1 > 0 ? n1 : 1, -1);
+    int nmatches = 0;
+    if (orbfe_search_for_triangulation(device, d1.data(), reinterpret_cast<const orbfe_keypoint*>(keys1.data()), uRight1 ? uRight1->data() : nullptr,
+                                       hasMapPoint1.empty() ? nullptr : hasMapPoint1.data(), n1, nA.data(), sA.data(), fA.data(), (int)nA.size(), d2.data(),
+                                       reinterpret_cast<const orbfe_keypoint*>(keys2.data()), uRight2 ? uRight2->data() : nullptr,
+                                       hasMapPoint2.empty() ? nullptr : hasMapPoint2.data(), n2, nB.data(), sB.data(), fB.data(), (int)nB.size(), F12, ep,
+                                       scaleFactors.data(), levelSigma2.data(), (int)std::min(scaleFactors.size(), levelSigma2.size()), thLow, bOnlyStereo ? 1 : 0,
+                                       bCoarse ? 1 : 0, checkOrientation ? 1 : 0, vMatches12.data(), &nmatches, rig) != ORBFE_OK)
+        throw std::runtime_error(std::string("orbfe_search_for_triangulation: ") + orbfe_last_error());
+    vMatches12.resize(n1);
     return nmatches;
 }
 

@@ -3,6 +3,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <string>
+#include <map>
 #include <vector>
 #include "orbfe_shim/ORBextractor.h"     // replaces the reference's include/ORBextractor.h (same public surface)
 #include "orbfe_shim/orbfe_matching.h"   // next to the reference's own ORBmatcher.h / Frame.h, which stay as they are
@@ -98,6 +99,22 @@ int main(int argc, char** argv) {
     const int ini = orbfe::SearchForInitialization(kL, dL, kR, dR, 0.f, 0.f, 64.f / W, 48.f / H, prevMatched, ini12, 100, 0.9f, true, ORBmatcher::TH_LOW);
     int iniCount = 0;
     for (int v : ini12) iniCount += v >= 0;
+    // SearchByBoW / SearchForTriangulation over std::map feature vectors (the shape of DBoW2::FeatureVector); the "vocabulary" here just groups
+    // features by the top six bits of their first descriptor byte, which is all the matchers need of one
+    std::map<unsigned, std::vector<unsigned>> fvL, fvR;
+    for (size_t i = 0; i < kL.size(); i++) fvL[dL.ptr<unsigned char>((int)i)[0] >> 2].push_back((unsigned)i);
+    for (size_t i = 0; i < kR.size(); i++) fvR[dR.ptr<unsigned char>((int)i)[0] >> 2].push_back((unsigned)i);
+    std::vector<unsigned char> allMp(kL.size(), 1), noMp;
+    std::vector<int> bowMatch, tri12;
+    const int bow = orbfe::SearchByBoW(dL, kL, fvL, allMp, dR, kR, fvR, -1, 0.7f, true, bowMatch);
+    long bowSum = 0;
+    for (size_t i = 0; i < bowMatch.size(); i++) bowSum += (long)(i + 1) * (bowMatch[i] + 1);
+    const float F12[9] = {0, 0, 0, 0, 0, -1, 0, 1, 0}, ep[2] = {-3000.f, 240.f};   // rectified pair: the epipolar line of a keypoint is its own row
+    std::vector<float> sigma2(left.GetScaleFactors().size());
+    for (size_t i = 0; i < sigma2.size(); i++) sigma2[i] = left.GetScaleFactors()[i] * left.GetScaleFactors()[i];
+    const int tri = orbfe::SearchForTriangulation(dL, kL, nullptr, noMp, fvL, dR, kR, nullptr, noMp, fvR, F12, ep, left.GetScaleFactors(), sigma2, false, false, true, tri12);
+    long triSum = 0;
+    for (size_t i = 0; i < tri12.size(); i++) triSum += (long)(i + 1) * (tri12[i] + 1);
     // a fisheye rig: both images with the lapping interval, then the whole Frame::ComputeStereoFishEyeMatches (src/Frame.cc:1119-1159)
     int fishMatches = 0;
     long fishSum = 0;
@@ -121,8 +138,8 @@ int main(int argc, char** argv) {
     }
     cv::Mat empty;
     const int rcEmpty = left(empty, mask, kR, dR, lap);
-    printf("shim n=%zu mono=%d monoR=%d levels=%d pyr0=%dx%d stereo=%d d01=%d top2acc=%d proj=%d projself=%d init=%d initcount=%d fish=%d fishsum=%ld empty=%d first=(%.1f,%.1f,%.3f,%d)\n",
-           kL.size(), monoL, monoR, left.GetLevels(), left.mvImagePyramid[0].cols, left.mvImagePyramid[0].rows, matched, d01, acc, proj, projSelf, ini, iniCount, fishMatches, fishSum, rcEmpty,
+    printf("shim n=%zu mono=%d monoR=%d levels=%d pyr0=%dx%d stereo=%d d01=%d top2acc=%d proj=%d projself=%d init=%d initcount=%d bow=%d bowsum=%ld tri=%d trisum=%ld fish=%d fishsum=%ld empty=%d first=(%.1f,%.1f,%.3f,%d)\n",
+           kL.size(), monoL, monoR, left.GetLevels(), left.mvImagePyramid[0].cols, left.mvImagePyramid[0].rows, matched, d01, acc, proj, projSelf, ini, iniCount, bow, bowSum, tri, triSum, fishMatches, fishSum, rcEmpty,
            kL[0].pt.x, kL[0].pt.y, kL[0].angle, kL[0].octave);
     return 0;
 }

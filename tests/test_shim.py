@@ -71,6 +71,19 @@ def test_shim_matches_oracle(tmp_path):
     assert nm > 1000
     im, _, inm = O.search_for_initialization(kL, dL, kR, dR, grid, np.stack([kL["x"], kL["y"]], 1), 100, 0.9, True)
     assert int(f["init"]) == inm and int(f["initcount"]) == int((im >= 0).sum()) and inm > 10
+    # SearchByBoW / SearchForTriangulation through the std::map wrappers: features grouped by the top six bits of their first descriptor byte
+    fv = lambda d: {int(g): np.nonzero((d[:, 0] >> 2) == g)[0].astype(np.int32) for g in sorted(set((d[:, 0] >> 2).tolist()))}  # noqa: E731
+    fvL, fvR = fv(dL), fv(dR)
+    bm, _, bnm = O.search_by_bow(dL, kL, fvL, np.ones(len(kL), np.uint8), dR, kR, fvR, 50, 0.7, True)
+    assert int(f["bow"]) == bnm, (f["bow"], bnm)
+    assert int(f["bowsum"]) == int(((np.arange(len(bm)) + 1).astype(np.int64) * (bm.astype(np.int64) + 1)).sum())
+    assert bnm > 5, bnm
+    sf = np.asarray(oL.scale_factors(), np.float32)
+    tm, tnm = O.search_for_triangulation(dL, kL, None, None, fvL, dR, kR, None, None, fvR, np.array([0, 0, 0, 0, 0, -1, 0, 1, 0], np.float32),
+                                         np.array([-3000.0, 240.0], np.float32), sf, (sf * sf).astype(np.float32), 50, False, False, True)
+    assert int(f["tri"]) == tnm, (f["tri"], tnm)
+    assert int(f["trisum"]) == int(((np.arange(len(tm)) + 1).astype(np.int64) * (tm.astype(np.int64) + 1)).sum())
+    assert tnm > 5, tnm
     # the fisheye rig of the probe: extraction with the lapping interval, knn-2 + 0.7, TriangulateMatches, depth test (src/Frame.cc:1119-1159)
     fL, fR = synth.stereo_pair(800, 512, 512)
     fp = (1500, 1.2, 8, 20, 7)
