@@ -549,6 +549,20 @@ __global__ void __launch_bounds__(SB_NT) k_triangulation_rotation(const int* __r
     if (tid == 0 && nmatches) nmatches[pr] = s_total;
 }
 
+/* a host feature vector must be well formed before it goes to a kernel that indexes with it: node ids strictly ascending (the kernels find a
+ * node by binary search), offsets non-decreasing from 0, at most n rows in all, every row inside the frame */
+static bool fv_well_formed(const int32_t* nodes, const int32_t* starts, const int32_t* feats, int nfv, int n) {
+    if (nfv == 0) return true;
+    if (starts[0] != 0) return false;
+    for (int e = 0; e < nfv; e++) {
+        if (starts[e + 1] < starts[e] || starts[e + 1] > n) return false;
+        if (e && nodes[e] <= nodes[e - 1]) return false;
+    }
+    for (int j = 0; j < starts[nfv]; j++)
+        if (feats[j] < 0 || feats[j] >= n) return false;
+    return true;
+}
+
 static int bow_norm_of(int scoring) { return scoring == 5 ? 0 : (scoring == 1 ? 2 : 1); }   /* ScoringObject.h:73-90 */
 
 extern "C" {
@@ -755,8 +769,8 @@ int orbfe_search_by_bow(int device, const uint8_t* desc_kf, const orbfe_keypoint
         orbfe_set_error("no usable CUDA device %d (found %d); this library has no CPU path", device, ndev);
         return ORBFE_E_CUDA;
     }
-    if (nfv_kf > S || nfv_f > S || (nfv_kf && fv_starts_kf[nfv_kf] > S) || (nfv_f && fv_starts_f[nfv_f] > S)) {
-        orbfe_set_error("feature vector longer than the frame");
+    if (nfv_kf > S || nfv_f > S || !fv_well_formed(fv_nodes_kf, fv_starts_kf, fv_feats_kf, nfv_kf, n_kf) || !fv_well_formed(fv_nodes_f, fv_starts_f, fv_feats_f, nfv_f, n_f)) {
+        orbfe_set_error("malformed feature vector (node ids ascending, offsets from 0, rows inside the frame)");
         return ORBFE_E_INVALID;
     }
     /* two frames (0 = keyframe, 1 = frame) in the strided layout of the batch entry point, laid out in the thread's staging block: inputs, then
@@ -849,7 +863,10 @@ int orbfe_search_for_triangulation(int device, const uint8_t* desc_1, const orbf
         (nfv_2 && (!fv_nodes_2 || !fv_starts_2 || !fv_feats_2))) { orbfe_set_error("bad argument"); return ORBFE_E_INVALID; }
     const int S = std::max(std::max(n_1, n_2), 1);
     if (S > BOW_MAXF) { orbfe_set_error("at most %d features per frame", BOW_MAXF); return ORBFE_E_CAPACITY; }
-    if (nfv_1 > S || nfv_2 > S || (nfv_1 && fv_starts_1[nfv_1] > S) || (nfv_2 && fv_starts_2[nfv_2] > S)) { orbfe_set_error("feature vector longer than the frame"); return ORBFE_E_INVALID; }
+    if (nfv_1 > S || nfv_2 > S || !fv_well_formed(fv_nodes_1, fv_starts_1, fv_feats_1, nfv_1, n_1) || !fv_well_formed(fv_nodes_2, fv_starts_2, fv_feats_2, nfv_2, n_2)) {
+        orbfe_set_error("malformed feature vector (node ids ascending, offsets from 0, rows inside the frame)");
+        return ORBFE_E_INVALID;
+    }
     if (nmatches) *nmatches = 0;
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev) {
@@ -928,8 +945,8 @@ static int frames_pack(const orbfe_host_frame* frames, int nframes, const int32_
             return ORBFE_E_INVALID;
         }
         if (fr.n > BOW_MAXF) { orbfe_set_error("at most %d features per frame", BOW_MAXF); return ORBFE_E_CAPACITY; }
-        if (fr.nfv > std::max(fr.n, 1) || (fr.nfv && (fr.fv_starts[fr.nfv] > fr.n || fr.fv_starts[fr.nfv] < 0))) {
-            orbfe_set_error("frame %d: feature vector longer than the frame", f);
+        if (fr.nfv > std::max(fr.n, 1) || !fv_well_formed(fr.fv_nodes, fr.fv_starts, fr.fv_feats, fr.nfv, fr.n)) {
+            orbfe_set_error("frame %d: malformed feature vector (node ids ascending, offsets from 0, rows inside the frame)", f);
             return ORBFE_E_INVALID;
         }
         S = std::max(S, fr.n);

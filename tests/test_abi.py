@@ -71,3 +71,25 @@ def test_host_libm_reproduces_the_trig_exception_table():
     n = C.c_int(0)
     assert L.orbfe_check_host_libm(C.byref(n)) == 0
     assert n.value == 96
+
+
+def test_frames_entry_points_refuse_malformed_feature_vectors_before_touching_a_device():
+    """orbfe_search_by_bow_frames / orbfe_search_for_triangulation_frames index device arrays with what the caller's FeatureVector says: rows
+    outside the frame, node ids out of order, offsets that do not start at 0 and pairs outside the frame list are refused on the host."""
+    import pytest
+    from orb_slam3_detailed_comments_kor_b200 import bow as B
+    from orb_slam3_detailed_comments_kor_b200._lib import OrbfeError
+    rng = np.random.RandomState(1)
+    desc = rng.randint(0, 256, (6, 32)).astype(np.uint8)
+    kps = np.zeros(6, _lib.KP_DTYPE)
+    good = {3: np.array([0, 1], np.int32), 7: np.array([2, 5], np.int32)}
+    for bad in ({3: np.array([0, 6], np.int32)},                                   # a row beyond the frame
+                {3: np.array([0, -1], np.int32)},
+                {7: np.array([0], np.int32), 3: np.array([1], np.int32)}):         # node ids not ascending
+        with pytest.raises(OrbfeError, match="malformed"):
+            B.search_by_bow_frames([dict(desc=desc, kps=kps, feat_vec=good), dict(desc=desc, kps=kps, feat_vec=bad)], [0], [1])
+    with pytest.raises(OrbfeError, match="outside the list"):
+        B.search_by_bow_frames([dict(desc=desc, kps=kps, feat_vec=good)], [0], [1])
+    with pytest.raises(OrbfeError, match="malformed"):
+        B.search_for_triangulation_frames([dict(desc=desc, kps=kps, feat_vec=good), dict(desc=desc, kps=kps, feat_vec={3: np.array([9], np.int32)})], [0], [1],
+                                          np.zeros((1, 9), np.float32), np.zeros((1, 2), np.float32), np.ones(8, np.float32), np.ones(8, np.float32))
