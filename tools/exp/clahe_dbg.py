@@ -1,3 +1,4 @@
+"""Experiment: which of the CLAHE parity cases differ between the GPU and the oracle, and where (development aid for the banded apply kernel)."""
 import sys, os
 ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))

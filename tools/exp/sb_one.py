@@ -1,4 +1,4 @@
-"""Experiment: k_search_by_bow variants (ORBFE_SB_VARIANT) on a batch of pairs (device entry) and on one pair (host entry)."""
+"""Experiment: one SearchByBoW pair on the device, five launches (the target of a single-launch ncu capture)."""
 import sys, os, time
 ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))

@@ -1,4 +1,4 @@
-"""Experiment: k_search_by_bow variants (ORBFE_SB_VARIANT) on a batch of pairs (device entry) and on one pair (host entry)."""
+"""Experiment: k_search_by_bow on a batch of pairs with deep competition (device entry), on 1 and 8 pairs, and on one pair through the host entry."""
 import sys, os, time
 ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
