@@ -55,6 +55,9 @@ def lib(fma=False):
     L.ref_search_by_projection_last_frame.argtypes = [vp, vp, C.c_int, C.c_int, vp, vp, vp, vp, vp, C.c_int, C.c_float, C.c_float, vp, vp, vp, vp, C.c_int, C.c_int,
                                                       vp, vp, vp, vp, vp, vp, C.c_float, C.c_int, C.c_int, vp]
     L.ref_search_by_projection_last_frame.restype = C.c_int
+    L.ref_search_by_projection_reloc.argtypes = [vp, vp, C.c_int, vp, vp, vp, vp, C.c_int, vp, vp, vp, C.c_int, vp, vp, vp, vp, vp, vp, vp, vp, C.c_float, C.c_int,
+                                                 C.c_int, vp]
+    L.ref_search_by_projection_reloc.restype = C.c_int
     L.ref_fuse.argtypes = [vp, vp, C.c_int, C.c_int, vp, vp, vp, vp, vp, vp, vp, C.c_int, C.c_float, vp, vp, C.c_int] + [vp] * 10 + [C.c_float, C.c_int, vp, vp]
     L.ref_fuse.restype = C.c_int
     L.ref_search_by_projection_sim3.argtypes = [vp, vp, C.c_int, vp, vp, vp, vp, C.c_int, vp, vp, C.c_int, vp, vp, vp, vp, vp, vp, vp, C.c_int, C.c_float, vp]
@@ -215,6 +218,23 @@ def search_by_projection_last_frame(kps, desc, n_left, u_right, obs_cur, grid4, 
     nm = lib().ref_search_by_projection_last_frame(p(kps), p(desc), len(kps), int(n_left), p(ur), p(oc), p(g), p(b), p(sf), len(sf), float(mbf), float(mb), p(Tcw), p(Trl),
                                                    p(cam4), p(kl), len(kl), int(n_left_last), p(hm), p(ol), p(w), p(om), p(dm), p(Tlw), float(th), int(mono),
                                                    int(check_orientation), p(owner))
+    return owner[:len(kps)], nm
+
+
+def search_by_projection_reloc(kps, desc, obs_cur, grid4, bounds4, scale_factors, Tcw, cam4, kps_kf, has_mp, bad, found, world, min_dist, max_dist, level, desc_mp,
+                               th, orb_dist, check_orientation):
+    """The reference's own ORBmatcher::SearchByProjection(CurrentFrame, pKF, sAlreadyFound, th, ORBdist) (Tracking::Relocalization) on arrays (see
+    ref_shim.cpp).  Returns (owner[n], nmatches)."""
+    c = lambda a, t: np.ascontiguousarray(a, t)  # noqa: E731
+    f = np.float32
+    kps, desc, oc = c(kps, KP_DTYPE), c(desc, np.uint8), c(obs_cur, np.int32)
+    g, b, sf, Tcw, cam4 = c(grid4, f), c(bounds4, f), c(scale_factors, f), c(np.asarray(Tcw, f).reshape(16), f), c(cam4, f)
+    kk, hm, bd, fd, w = c(kps_kf, KP_DTYPE), c(has_mp, np.uint8), c(bad, np.uint8), c(found, np.uint8), c(world, f)
+    mn, mx, lv, dm = c(min_dist, f), c(max_dist, f), c(level, np.int32), c(desc_mp, np.uint8)
+    owner = np.zeros(max(len(kps), 1), np.int32)
+    nm = lib().ref_search_by_projection_reloc(_ptr(kps), _ptr(desc), len(kps), _ptr(oc), _ptr(g), _ptr(b), _ptr(sf), len(sf), _ptr(Tcw), _ptr(cam4), _ptr(kk), len(kk),
+                                              _ptr(hm), _ptr(bd), _ptr(fd), _ptr(w), _ptr(mn), _ptr(mx), _ptr(lv), _ptr(dm), float(th), int(orb_dist),
+                                              int(check_orientation), _ptr(owner))
     return owner[:len(kps)], nm
 
 

@@ -108,6 +108,7 @@ namespace ORB_SLAM3 {
 
 /* only what the cut-out bodies name: include/MapPoint.h (isBad), include/KeyFrame.h and include/Frame.h (the members below) */
 class KeyFrame;
+class Frame;
 class MapPoint {
 public:
     bool bad = false;
@@ -139,6 +140,7 @@ public:
     float GetMaxDistanceInvariance() { return mfMaxDistance; }
     cv::Mat GetNormal() { return mNormalVector.clone(); }
     int PredictScale(const float&, KeyFrame*) { return predictedLevel; }
+    int PredictScale(const float&, Frame*) { return predictedLevel; }
     void AddObservation(KeyFrame*, int idx) { fusedRow = idx; fusedHow = 1; }
     void Replace(MapPoint* other) {   /* one of the two is the candidate map point, the other the one the keypoint row holds (rowIndex >= 0) */
         MapPoint* q = rowIndex < 0 ? this : other;
@@ -228,6 +230,7 @@ public:
     int SearchForInitialization(Frame& F1, Frame& F2, std::vector<cv::Point2f>& vbPrevMatched, std::vector<int>& vnMatches12, int windowSize = 10);
     int SearchForTriangulation(KeyFrame* pKF1, KeyFrame* pKF2, cv::Mat F12, std::vector<std::pair<size_t, size_t>>& vMatchedPairs, const bool bOnlyStereo, const bool bCoarse = false);
     int SearchByProjection(Frame& CurrentFrame, const Frame& LastFrame, const float th, const bool bMono);
+    int SearchByProjection(Frame& CurrentFrame, KeyFrame* pKF, const std::set<MapPoint*>& sAlreadyFound, const float th, const int ORBdist);
     int Fuse(KeyFrame* pKF, const std::vector<MapPoint*>& vpMapPoints, const float th = 3.0, const bool bRight = false);
     int SearchByProjection(KeyFrame* pKF, cv::Mat Scw, const std::vector<MapPoint*>& vpPoints, std::vector<MapPoint*>& vpMatched, int th, float ratioHamming = 1.0);
     int Fuse(KeyFrame* pKF, cv::Mat Scw, const std::vector<MapPoint*>& vpPoints, float th, std::vector<MapPoint*>& vpReplacePoint);
@@ -254,6 +257,7 @@ const int ORBmatcher::HISTO_LENGTH = 30;   /* src/ORBmatcher.cc:38 */
 #include "_ref/ORBmatcher_SearchForTriangulation.inc"
 #include "_ref/ORBmatcher_SearchByProjectionLastFrame.inc"
 #include "_ref/KeyFrame_grid.inc"
+#include "_ref/ORBmatcher_SearchByProjectionReloc.inc"
 #include "_ref/ORBmatcher_Fuse.inc"
 #include "_ref/ORBmatcher_SearchByProjectionSim3.inc"
 #include "_ref/ORBmatcher_FuseSim3.inc"
@@ -587,6 +591,60 @@ int ref_search_by_projection_last_frame(const orc_keypoint* kps, const uint8_t* 
     }
     ORBmatcher matcher(0.9f, check_orientation != 0);
     const int nm = matcher.SearchByProjection(F, Last, th, mono != 0);
+    for (int i = 0; i < n; i++) {
+        MapPoint* p = F.mvpMapPoints[i];
+        owner[i] = !p ? -1 : (p >= initial.data() && p < initial.data() + n) ? -2 : (int32_t)(p - store.data());
+    }
+    return nm;
+}
+
+/* ORBmatcher::SearchByProjection(CurrentFrame, pKF, sAlreadyFound, th, ORBdist) (src/ORBmatcher.cc:2421-2543, Tracking::Relocalization) on arrays.
+ *   current frame as in ref_search_by_projection_last_frame (pinhole, no second camera): kps / desc [n], obs_cur [n] (-1: the row holds no map point),
+ *   grid4, bounds4, scale_factors, Tcw [16], cam4;
+ *   keyframe: nk rows with the angle in kps_kf; per row has_mp, bad, found (the point is in sAlreadyFound), world [3], min_dist / max_dist (the
+ *   distance-invariance interval), level (what PredictScale returns), desc_mp [32].
+ * owner[row] = index of the keyframe row whose map point the row holds afterwards, -2 = the initial one, -1 = none.  Returns nmatches. */
+int ref_search_by_projection_reloc(const orc_keypoint* kps, const uint8_t* desc, int n, const int32_t* obs_cur, const float* grid4, const float* bounds4,
+                                   const float* scale_factors, int nlevels, const float* Tcw, const float* cam4, const orc_keypoint* kps_kf, int nk,
+                                   const uint8_t* has_mp, const uint8_t* bad, const uint8_t* found, const float* world, const float* min_dist, const float* max_dist,
+                                   const int32_t* level, const uint8_t* desc_mp, float th, int orb_dist, int check_orientation, int32_t* owner) {
+    using namespace ORB_SLAM3;
+    ArenaScope scope;
+    Frame F;
+    KeyFrame kf;
+    Frame::mnMinX = grid4[0]; Frame::mnMinY = grid4[1]; Frame::mfGridElementWidthInv = grid4[2]; Frame::mfGridElementHeightInv = grid4[3];
+    Frame::mnMaxX = bounds4[1]; Frame::mnMaxY = bounds4[3];
+    Pinhole camera(std::vector<float>(cam4, cam4 + 4));
+    F.N = n; F.Nleft = -1; F.mpCamera = &camera;
+    F.mDescriptors = cv::Mat(n, 32, CV_8UC1, (void*)desc, 32);
+    F.mvKeysUn.resize(n);
+    if (n) std::memcpy((void*)F.mvKeysUn.data(), kps, sizeof(orc_keypoint) * n);
+    F.mvKeys = F.mvKeysUn;
+    F.mvuRight.assign(n, -1.f);
+    F.mvScaleFactors.assign(scale_factors, scale_factors + nlevels);
+    F.mTcw = mat_from(Tcw, 4, 4);
+    F.AssignFeaturesToGrid();
+    std::vector<MapPoint> initial(n);
+    F.mvpMapPoints.assign(n, nullptr);
+    for (int i = 0; i < n; i++)
+        if (obs_cur[i] >= 0) { initial[i].nObs = obs_cur[i]; F.mvpMapPoints[i] = &initial[i]; }
+    kf.N = nk;
+    kf.mvKeysUn.resize(nk);
+    if (nk) std::memcpy((void*)kf.mvKeysUn.data(), kps_kf, sizeof(orc_keypoint) * nk);
+    std::vector<MapPoint> store(nk);
+    kf.mvpMapPoints.assign(nk, nullptr);
+    std::set<MapPoint*> already;
+    for (int i = 0; i < nk; i++) {
+        store[i].bad = bad[i] != 0;
+        store[i].mWorldPos = mat_from(world + 3 * i, 3, 1);
+        store[i].mfMinDistance = min_dist[i]; store[i].mfMaxDistance = max_dist[i];
+        store[i].predictedLevel = level[i];
+        store[i].mDescriptor = cv::Mat(1, 32, CV_8UC1, (void*)(desc_mp + (size_t)i * 32), 32);
+        if (has_mp[i]) kf.mvpMapPoints[i] = &store[i];
+        if (found[i]) already.insert(&store[i]);
+    }
+    ORBmatcher matcher(0.9f, check_orientation != 0);
+    const int nm = matcher.SearchByProjection(F, &kf, already, th, orb_dist);
     for (int i = 0; i < n; i++) {
         MapPoint* p = F.mvpMapPoints[i];
         owner[i] = !p ? -1 : (p >= initial.data() && p < initial.data() + n) ? -2 : (int32_t)(p - store.data());

@@ -451,6 +451,72 @@ def test_search_by_projection_last_frame_equals_reference(name, kw, motion, mono
     assert (pm["status"] == 7).sum() > 0                                    # the rotation check removes some
 
 
+@pytest.mark.parametrize("name,kw,th,orb_dist", [("coarse", dict(seed=81, n=1100), 10.0, 100), ("fine", dict(seed=82, n=900), 3.0, 64),
+                                                 ("crowded", dict(seed=83, n=60), 10.0, 100)])
+def test_search_by_projection_relocalization_equals_reference(name, kw, th, orb_dist):
+    """ORBmatcher::SearchByProjection(CurrentFrame, pKF, sAlreadyFound, th, ORBdist) (src/ORBmatcher.cc:2421-2543; Tracking::Relocalization calls it
+    with (10, 100) and (3, 64)) — the reference's own body, compiled — against the oracle driven through the query list INTEGRATION.md 5a
+    prescribes for this overload: best-only queries that always occupy what they take, levels [predicted - 1, predicted + 1], th_high = ORBdist,
+    every row of the current frame that holds a map point occupied from the start, the points of sAlreadyFound / bad points / points outside the
+    image or their distance interval left out, the rotation check on.  As in the frame-to-frame test the pose is the identity and the camera a
+    unit pinhole, so that what is compared is the search, not the projection arithmetic that stays with the caller."""
+    from orb_slam3_detailed_comments_kor_b200.synth import projection_cases as PC
+    f32 = np.float32
+    c = PC.make_case(nq=1, **kw)
+    kps, desc, grid = c["kps"], c["desc"], c["grid"]
+    n = len(kps)
+    W, H = 752.0, 480.0
+    rng = np.random.RandomState(kw["seed"] + 1000)
+    scale = np.array([f32(1.2) ** i for i in range(8)], f32)
+    obs_cur = np.where(rng.uniform(size=n) < 0.15, rng.randint(0, 2, n), -1).astype(np.int32)      # some rows hold a point, with or without observations
+    nk = 800
+    kk = np.zeros(nk, PC.KP_DTYPE)
+    level = np.minimum(rng.geometric(0.35, nk) - 1, 7).astype(np.int32)
+    turn = rng.uniform(-40, 40)
+    hot = rng.choice(n, min(12, n), replace=False)
+    tgt = np.where(rng.uniform(size=nk) < (0.6 if name == "crowded" else 0.15), hot[rng.randint(0, len(hot), nk)], rng.randint(0, n, nk))
+    radius = (f32(th) * scale[level]).astype(f32)
+    x = (kps["x"][tgt] + rng.uniform(-0.6, 0.6, nk) * radius).astype(f32)
+    y = (kps["y"][tgt] + rng.uniform(-0.6, 0.6, nk) * radius).astype(f32)
+    far = rng.uniform(size=nk) < 0.1
+    x[far] = rng.uniform(-40, W + 40, int(far.sum())).astype(f32); y[far] = rng.uniform(-40, H + 40, int(far.sum())).astype(f32)
+    kk["angle"] = np.where(rng.uniform(size=nk) < 0.8, kps["angle"][tgt] + turn + rng.uniform(-4, 4, nk), rng.uniform(0, 360, nk)).astype(f32) % f32(360)
+    world = np.stack([x, y, np.ones(nk, f32)], 1).astype(f32)               # identity pose, unit pinhole: the projection is (x, y) exactly
+    has_mp = (rng.uniform(size=nk) < 0.9).astype(np.uint8)
+    bad = (rng.uniform(size=nk) < 0.05).astype(np.uint8)
+    found = (rng.uniform(size=nk) < 0.1).astype(np.uint8)
+    out_of_range = rng.uniform(size=nk) < 0.06                              # the distance-invariance interval misses the point
+    min_dist = np.where(out_of_range & (rng.uniform(size=nk) < 0.5), 1e6, 0.0).astype(f32)
+    max_dist = np.where(out_of_range & (min_dist == 0), 1e-3, 1e6).astype(f32)
+    desc_mp = desc[tgt].copy()
+    for i in range(nk):
+        for b in rng.choice(256, size=int(rng.randint(0, 90)), replace=False):
+            desc_mp[i, b >> 3] ^= np.uint8(1 << (b & 7))
+    bounds = np.array([0, W, 0, H], f32)
+    got, rnm = Rf.search_by_projection_reloc(kps, desc, obs_cur, grid, bounds, scale, np.eye(4, dtype=f32), [1, 1, 0, 0], kk, has_mp, bad, found, world, min_dist,
+                                             max_dist, level, desc_mp, th, orb_dist, True)
+    q, qd, src = [], [], []
+    for i in range(nk):
+        if not has_mp[i] or bad[i] or found[i] or out_of_range[i]:
+            continue
+        if x[i] < 0 or x[i] > W or y[i] < 0 or y[i] > H:
+            continue
+        o = int(level[i])
+        q.append((x[i], y[i], radius[i], f32(0), o - 1, o + 1, PC.PQ_BEST_ONLY | PC.PQ_BLOCKS, kk["angle"][i])); qd.append(desc_mp[i]); src.append(i)
+    q = np.array(q, PC.PROJ_QUERY_DTYPE)
+    pm, _, nm = O.search_by_projection(kps, desc, q, np.stack(qd), grid, taken=(obs_cur >= 0).astype(np.uint8), th_high=orb_dist, nnratio=0.9, check_orientation=True)
+    want = np.where(obs_cur >= 0, -2, -1).astype(np.int32)
+    for k in range(len(q)):
+        if pm["status"][k] in (1, 7):                                     # accepted, or accepted and later removed by the rotation check
+            want[int(pm["best_idx"][k])] = src[k]
+    for k in range(len(q)):
+        if pm["status"][k] == 7:
+            want[int(pm["best_idx"][k])] = -1
+    assert np.array_equal(got, want), "%s: %d rows differ" % (name, int((got != want).sum()))
+    assert rnm == nm and nm > 15
+    assert (pm["status"] == 7).sum() > 0                                    # the rotation check removes some
+
+
 @pytest.mark.parametrize("name,kw,right", [("stereo", dict(seed=71, n=900, stereo_gate=True), False), ("mono", dict(seed=72, n=700), False),
                                            ("rig_left", dict(seed=73, n=900, fisheye=True), False), ("rig_right", dict(seed=74, n=900, fisheye=True), True)])
 def test_fuse_equals_reference(name, kw, right):
