@@ -60,7 +60,7 @@ def lib(fma=False):
     L.ref_search_by_projection_reloc.restype = C.c_int
     L.ref_fuse.argtypes = [vp, vp, C.c_int, C.c_int, vp, vp, vp, vp, vp, vp, vp, C.c_int, C.c_float, vp, vp, C.c_int] + [vp] * 10 + [C.c_float, C.c_int, vp, vp]
     L.ref_fuse.restype = C.c_int
-    L.ref_search_by_projection_sim3.argtypes = [vp, vp, C.c_int, vp, vp, vp, vp, C.c_int, vp, vp, C.c_int, vp, vp, vp, vp, vp, vp, vp, C.c_int, C.c_float, vp]
+    L.ref_search_by_projection_sim3.argtypes = [vp, vp, C.c_int, vp, vp, vp, vp, C.c_int, vp, vp, C.c_int, vp, vp, vp, vp, vp, vp, vp, C.c_int, C.c_float, vp, vp, vp]
     L.ref_search_by_projection_sim3.restype = C.c_int
     L.ref_fuse_sim3.argtypes = [vp, vp, C.c_int, vp, vp, vp, vp, C.c_int, vp, vp, C.c_int, vp, vp, vp, vp, vp, vp, vp, C.c_float, vp, vp]
     L.ref_fuse_sim3.restype = C.c_int
@@ -255,15 +255,21 @@ def fuse(kps, desc, n_left, u_right, row_obs, row_bad, grid4, bounds4, scale_fac
     return row[:nmp], how[:nmp], nf
 
 
-def search_by_projection_sim3(kps, desc, matched_in, grid4, bounds4, scale_factors, cam4, Scw, mp, th, ratio_hamming):
-    """The reference's own ORBmatcher::SearchByProjection(pKF, Scw, vpPoints, vpMatched, th, ratioHamming) on arrays.  Returns (owner[n], nmatches)."""
+def search_by_projection_sim3(kps, desc, matched_in, grid4, bounds4, scale_factors, cam4, Scw, mp, th, ratio_hamming, point_kf=None):
+    """The reference's own ORBmatcher::SearchByProjection(pKF, Scw, vpPoints, vpMatched, th, ratioHamming) on arrays.  Returns (owner[n], nmatches);
+    with point_kf (the keyframe number of every candidate) the second overload (vpPointsKFs / vpMatchedKF) and (owner, owner_kf[n], nmatches)."""
     c = lambda a, t: np.ascontiguousarray(a, t)  # noqa: E731
     f = np.float32
     kps, desc, mi, g, b, sf, cam4, Scw = c(kps, KP_DTYPE), c(desc, np.uint8), c(matched_in, np.int32), c(grid4, f), c(bounds4, f), c(scale_factors, f), c(cam4, f), c(np.asarray(Scw, f).reshape(16), f)
     arrs = [c(mp["bad"], np.uint8), c(mp["world"], f), c(mp["normal"], f), c(mp["min_dist"], f), c(mp["max_dist"], f), c(mp["level"], np.int32), c(mp["desc"], np.uint8)]
     owner = np.zeros(max(len(kps), 1), np.int32)
+    pk = None if point_kf is None else c(point_kf, np.int32)
+    okf = np.full(max(len(kps), 1), -1, np.int32)
     nm = lib().ref_search_by_projection_sim3(_ptr(kps), _ptr(desc), len(kps), _ptr(mi), _ptr(g), _ptr(b), _ptr(sf), len(sf), _ptr(cam4), _ptr(Scw), len(arrs[0]),
-                                             *[_ptr(a) for a in arrs], int(th), float(ratio_hamming), _ptr(owner))
+                                             *[_ptr(a) for a in arrs], int(th), float(ratio_hamming), _ptr(owner), _ptr(pk) if pk is not None else None,
+                                             _ptr(okf) if pk is not None else None)
+    if pk is not None:
+        return owner[:len(kps)], okf[:len(kps)], nm
     return owner[:len(kps)], nm
 
 

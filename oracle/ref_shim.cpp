@@ -233,6 +233,8 @@ public:
     int SearchByProjection(Frame& CurrentFrame, KeyFrame* pKF, const std::set<MapPoint*>& sAlreadyFound, const float th, const int ORBdist);
     int Fuse(KeyFrame* pKF, const std::vector<MapPoint*>& vpMapPoints, const float th = 3.0, const bool bRight = false);
     int SearchByProjection(KeyFrame* pKF, cv::Mat Scw, const std::vector<MapPoint*>& vpPoints, std::vector<MapPoint*>& vpMatched, int th, float ratioHamming = 1.0);
+    int SearchByProjection(KeyFrame* pKF, cv::Mat Scw, const std::vector<MapPoint*>& vpPoints, const std::vector<KeyFrame*>& vpPointsKFs,
+                           std::vector<MapPoint*>& vpMatched, std::vector<KeyFrame*>& vpMatchedKF, int th, float ratioHamming = 1.0);
     int Fuse(KeyFrame* pKF, cv::Mat Scw, const std::vector<MapPoint*>& vpPoints, float th, std::vector<MapPoint*>& vpReplacePoint);
     int SearchBySim3(KeyFrame* pKF1, KeyFrame* pKF2, std::vector<MapPoint*>& vpMatches12, const float& s12, const cv::Mat& R12, const cv::Mat& t12, const float th);
     float RadiusByViewingCos(const float& viewCos);
@@ -260,6 +262,7 @@ const int ORBmatcher::HISTO_LENGTH = 30;   /* src/ORBmatcher.cc:38 */
 #include "_ref/ORBmatcher_SearchByProjectionReloc.inc"
 #include "_ref/ORBmatcher_Fuse.inc"
 #include "_ref/ORBmatcher_SearchByProjectionSim3.inc"
+#include "_ref/ORBmatcher_SearchByProjectionSim3KFs.inc"
 #include "_ref/ORBmatcher_FuseSim3.inc"
 #include "_ref/ORBmatcher_SearchBySim3.inc"
 
@@ -720,7 +723,9 @@ int ref_fuse(const orc_keypoint* kps, const uint8_t* desc, int n, int n_left, co
 int ref_search_by_projection_sim3(const orc_keypoint* kps, const uint8_t* desc, int n, const int32_t* matched_in, const float* grid4, const float* bounds4,
                                   const float* scale_factors, int nlevels, const float* cam4, const float* Scw, int nmp, const uint8_t* bad, const float* world,
                                   const float* normal, const float* min_dist, const float* max_dist, const int32_t* level, const uint8_t* desc_mp, int th,
-                                  float ratio_hamming, int32_t* owner) {
+                                  float ratio_hamming, int32_t* owner, const int32_t* point_kf, int32_t* owner_kf) {
+    /* point_kf != NULL: the second overload (src/ORBmatcher.cc:588-704), vpPointsKFs[i] = keyframe number point_kf[i]; owner_kf[row] = the number
+     * vpMatchedKF[row] ends up with (-1: untouched) */
     using namespace ORB_SLAM3;
     ArenaScope scope;
     Frame F;
@@ -758,7 +763,17 @@ int ref_search_by_projection_sim3(const orc_keypoint* kps, const uint8_t* desc, 
     std::vector<MapPoint*> matched(n, nullptr);
     for (int i = 0; i < n; i++) matched[i] = matched_in[i] == -1 ? nullptr : matched_in[i] == -2 ? &other : &store[matched_in[i]];
     ORBmatcher matcher(0.75f, true);
-    const int nm = matcher.SearchByProjection(&kf, mat_from(Scw, 4, 4), vp, matched, th, ratio_hamming);
+    int nm;
+    if (point_kf) {
+        int nkf = 1;
+        for (int i = 0; i < nmp; i++) nkf = std::max(nkf, point_kf[i] + 1);
+        std::vector<KeyFrame> kfs(nkf);
+        std::vector<KeyFrame*> pointKFs(nmp), matchedKF(n, nullptr);
+        for (int i = 0; i < nmp; i++) pointKFs[i] = &kfs[point_kf[i]];
+        nm = matcher.SearchByProjection(&kf, mat_from(Scw, 4, 4), vp, pointKFs, matched, matchedKF, th, ratio_hamming);
+        for (int i = 0; i < n; i++) owner_kf[i] = matchedKF[i] ? (int32_t)(matchedKF[i] - kfs.data()) : -1;
+    } else
+        nm = matcher.SearchByProjection(&kf, mat_from(Scw, 4, 4), vp, matched, th, ratio_hamming);
     for (int i = 0; i < n; i++) owner[i] = !matched[i] ? -1 : matched[i] == &other ? -2 : (int32_t)(matched[i] - store.data());
     return nm;
 }

@@ -637,6 +637,16 @@ def test_search_by_projection_sim3_equals_reference(seed, ratio):
             want[int(pm["best_idx"][k])] = src[k]
     assert np.array_equal(got, want), "%d rows differ" % int((got != want).sum())
     assert rnm == nm and nm > 100
+    # the second overload (src/ORBmatcher.cc:588-704, LoopClosing::FindMatchesByProjection): the same search with its own projection expression
+    # (x * invz instead of the camera's division: both exact here), plus vpMatchedKF[bestIdx] = vpPointsKFs[iMP] — the caller's bookkeeping on the
+    # accepted best_idx
+    point_kf = rng.randint(0, 7, nmp).astype(np.int32)
+    got2, kf2, rnm2 = Rf.search_by_projection_sim3(kps, desc, matched_in, grid, [0, W, 0, H], scale, [1, 1, 0, 0], Scw, mp, th, ratio, point_kf=point_kf)
+    want_kf = np.full(n, -1, np.int32)
+    for k in range(len(q)):
+        if pm["accepted"][k]:
+            want_kf[int(pm["best_idx"][k])] = point_kf[src[k]]
+    assert np.array_equal(got2, want) and rnm2 == nm and np.array_equal(kf2, want_kf)
 
 
 @pytest.mark.parametrize("seed", [91, 92])
