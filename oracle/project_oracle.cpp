@@ -10,7 +10,8 @@
  * on plain arrays, in the reference's serial order (a map point that was matched blocks its keypoint for the map points
  * after it).  No third-party arithmetic is involved.  PINNED against the reference's own bodies, cut out of src/ORBmatcher.cc, src/Frame.cc
  * and src/KeyFrame.cc and compiled into oracle/_ref/liborb_ref.so (tests/test_ref_pinned.py, tests/test_initialization.py): the
- * SearchLocalPoints, frame-to-frame and Sim3 SearchByProjection overloads, both Fuse functions, SearchBySim3 and SearchForInitialization;
+ * SearchLocalPoints, frame-to-frame, relocalisation and both Sim3 SearchByProjection overloads, both Fuse functions, SearchBySim3 and
+ * SearchForInitialization;
  * an independent Python restatement in tools/make_goldens.py (tests/golden/projection.npz) besides. */
 #include <cmath>
 #include <cstdint>
