@@ -55,6 +55,8 @@ def lib(fma=False):
     L.ref_search_by_projection_last_frame.argtypes = [vp, vp, C.c_int, C.c_int, vp, vp, vp, vp, vp, C.c_int, C.c_float, C.c_float, vp, vp, vp, vp, C.c_int, C.c_int,
                                                       vp, vp, vp, vp, vp, vp, C.c_float, C.c_int, C.c_int, vp]
     L.ref_search_by_projection_last_frame.restype = C.c_int
+    L.ref_fisheye_stereo.argtypes = [vp, vp, C.c_int, C.c_int, vp, vp, C.c_int, C.c_int, vp, vp, vp, vp, vp, C.c_int, vp, vp, vp, vp]
+    L.ref_fisheye_stereo.restype = C.c_int
     L.ref_search_by_projection_reloc.argtypes = [vp, vp, C.c_int, vp, vp, vp, vp, C.c_int, vp, vp, vp, C.c_int, vp, vp, vp, vp, vp, vp, vp, vp, C.c_float, C.c_int,
                                                  C.c_int, vp]
     L.ref_search_by_projection_reloc.restype = C.c_int
@@ -219,6 +221,20 @@ def search_by_projection_last_frame(kps, desc, n_left, u_right, obs_cur, grid4, 
                                                    p(cam4), p(kl), len(kl), int(n_left_last), p(hm), p(ol), p(w), p(om), p(dm), p(Tlw), float(th), int(mono),
                                                    int(check_orientation), p(owner))
     return owner[:len(kps)], nm
+
+
+def fisheye_stereo(kps_l, desc_l, mono_l, kps_r, desc_r, mono_r, cam1, cam2, Rlr, tlr, level_sigma2):
+    """The reference's own Frame::ComputeStereoFishEyeMatches (src/Frame.cc:1119-1159) on the two images' extractor outputs.  Returns
+    (mvLeftToRightMatch[nl], mvRightToLeftMatch[nr], mvDepth[nl], mvStereo3Dpoints[nl, 3] with 0 where empty, matches kept)."""
+    c = lambda a, t: np.ascontiguousarray(a, t)  # noqa: E731
+    f = np.float32
+    kl, dl, kr, dr = c(kps_l, KP_DTYPE), c(desc_l, np.uint8), c(kps_r, KP_DTYPE), c(desc_r, np.uint8)
+    c1, c2, R, t, ls = c(cam1, f), c(cam2, f), c(np.asarray(Rlr, f).reshape(9), f), c(tlr, f), c(level_sigma2, f)
+    l2r, r2l = np.zeros(max(len(kl), 1), np.int32), np.zeros(max(len(kr), 1), np.int32)
+    depth, p3d = np.zeros(max(len(kl), 1), f), np.zeros((max(len(kl), 1), 3), f)
+    kept = lib().ref_fisheye_stereo(_ptr(kl), _ptr(dl), len(kl), int(mono_l), _ptr(kr), _ptr(dr), len(kr), int(mono_r), _ptr(c1), _ptr(c2), _ptr(R), _ptr(t), _ptr(ls),
+                                    len(ls), _ptr(l2r), _ptr(r2l), _ptr(depth), _ptr(p3d))
+    return l2r[:len(kl)], r2l[:len(kr)], depth[:len(kl)], p3d[:len(kl)], kept
 
 
 def search_by_projection_reloc(kps, desc, obs_cur, grid4, bounds4, scale_factors, Tcw, cam4, kps_kf, has_mp, bad, found, world, min_dist, max_dist, level, desc_mp,

@@ -149,6 +149,35 @@ public:
     }
 };
 
+}  // namespace ORB_SLAM3 (reopened below)
+namespace cv {
+/* cv::BFMatcher(cv::NORM_HAMMING)::knnMatch as Frame::ComputeStereoFishEyeMatches uses it — OpenCV's code, restated: per query row the k smallest
+ * Hamming distances in ascending order, the lower train row first among equals (what orc_knn2_ratio keeps too; pinned against cv2.BFMatcher by
+ * the knn goldens, tests/test_oracle_golden.py) */
+struct DMatch { int queryIdx, trainIdx, imgIdx; float distance; };
+enum { NORM_HAMMING = 6 };
+class BFMatcher {
+public:
+    explicit BFMatcher(int = NORM_HAMMING) {}
+    void knnMatch(const Mat& q, const Mat& t, std::vector<std::vector<DMatch>>& matches, int k) const {
+        matches.assign(q.rows, std::vector<DMatch>());
+        for (int i = 0; i < q.rows; i++) {
+            std::vector<std::pair<int, int>> best;   /* (distance, train row), ascending, at most k */
+            for (int j = 0; j < t.rows; j++) {
+                int d = 0;
+                const unsigned char *a = q.ptr<unsigned char>(i), *b = t.ptr<unsigned char>(j);
+                for (int c = 0; c < 32; c++) d += __builtin_popcount((unsigned)(a[c] ^ b[c]));
+                size_t pos = best.size();
+                while (pos > 0 && d < best[pos - 1].first) pos--;
+                if ((int)pos < k) { best.insert(best.begin() + pos, std::make_pair(d, j)); if ((int)best.size() > k) best.pop_back(); }
+            }
+            for (const auto& e : best) matches[i].push_back(DMatch{i, e.second, 0, (float)e.first});
+        }
+    }
+};
+}  // namespace cv
+namespace ORB_SLAM3 {
+
 #define FRAME_GRID_ROWS 48 /* include/Frame.h:37-38 */
 #define FRAME_GRID_COLS 64
 
@@ -164,7 +193,14 @@ public:
     std::vector<float> mvuRight, mvDepth;
     std::vector<float> mvScaleFactors, mvInvScaleFactors;
     DBoW2::FeatureVector mFeatVec;
-    void* mpCamera2 = nullptr;   /* GeometricCamera*: only tested against NULL by the bodies taken here */
+    GeometricCamera* mpCamera2 = nullptr;
+    /* what ComputeStereoFishEyeMatches reads and fills on top (include/Frame.h) */
+    void ComputeStereoFishEyeMatches();
+    int monoLeft = 0, monoRight = 0, Nright = 0, mnCloseMPs = 0;
+    std::vector<cv::Mat> mvStereo3Dpoints;
+    std::vector<float> mvLevelSigma2;
+    cv::Mat mRlr, mtlr;
+    cv::BFMatcher BFmatcher;
     /* the grid of include/Frame.h:187-189,232-235,296 and what SearchByProjection touches */
     std::vector<size_t> GetFeaturesInArea(const float& x, const float& y, const float& r, const int minLevel = -1, const int maxLevel = -1,
                                           const bool bRight = false) const;
@@ -250,6 +286,7 @@ const int ORBmatcher::HISTO_LENGTH = 30;   /* src/ORBmatcher.cc:38 */
 #include "_ref/ORBmatcher_constants.inc"
 #include "_ref/ORBmatcher_DescriptorDistance.inc"
 #include "_ref/Frame_ComputeStereoMatches.inc"
+#include "_ref/Frame_ComputeStereoFishEyeMatches.inc"
 #include "_ref/ORBmatcher_ComputeThreeMaxima.inc"
 #include "_ref/ORBmatcher_SearchByBoW.inc"
 #include "_ref/Frame_grid.inc"
@@ -419,7 +456,7 @@ int ref_search_by_bow(const uint8_t* desc_kf, const orc_keypoint* kps_kf, int n_
         F.N = n_f;
         F.Nleft = n_left_f;
         static int rig_marker;
-        if (n_left_f >= 0) F.mpCamera2 = &rig_marker;   /* a fisheye rig: the frame has a second camera */
+        if (n_left_f >= 0) F.mpCamera2 = reinterpret_cast<GeometricCamera*>(&rig_marker);   /* a fisheye rig: the frame has a second camera */
         F.mDescriptors = cv::Mat(n_f, 32, CV_8UC1, (void*)desc_f, 32);
         if (n_left_f < 0) F.mvKeysUn = F.mvKeys = keys_of(kps_f, n_f);
         else { F.mvKeys = keys_of(kps_f, n_left_f); F.mvKeysRight = keys_of(kps_f + n_left_f, n_f - n_left_f); }
@@ -540,6 +577,38 @@ void ref_kb8_triangulate_matches(const float* cam1, const float* cam2, const flo
         depth[i] = c1.TriangulateMatches(&c2, k1, k2, R, t, sigma1[i], sigma2[i], p);
         for (int k = 0; k < 3; k++) p3d[3 * i + k] = p.empty() ? 0.f : p.at<float>(k);
     }
+}
+
+/* Frame::ComputeStereoFishEyeMatches (src/Frame.cc:1119-1159) on the two images' keypoints and descriptors (the extractor's output order: the
+ * monocular part first, then the rows inside the lapping interval): left_to_right [nl], right_to_left [nr], depth [nl], p3d [nl][3] (0 where
+ * mvStereo3Dpoints stays empty).  cam1 / cam2 = mvParameters of the two KannalaBrandt8 cameras, Rlr / tlr = mRlr / mtlr.  Returns the matches kept. */
+int ref_fisheye_stereo(const orc_keypoint* kps_l, const uint8_t* desc_l, int nl, int mono_l, const orc_keypoint* kps_r, const uint8_t* desc_r, int nr, int mono_r,
+                       const float* cam1, const float* cam2, const float* Rlr, const float* tlr, const float* level_sigma2, int nlevels, int32_t* left_to_right,
+                       int32_t* right_to_left, float* depth, float* p3d) {
+    using namespace ORB_SLAM3;
+    ArenaScope scope;
+    Frame F;
+    KannalaBrandt8 c1(std::vector<float>(cam1, cam1 + 8)), c2(std::vector<float>(cam2, cam2 + 8));
+    F.mpCamera = &c1; F.mpCamera2 = &c2;
+    F.Nleft = nl; F.Nright = nr; F.monoLeft = mono_l; F.monoRight = mono_r;
+    F.mvKeys.resize(nl); F.mvKeysRight.resize(nr);
+    if (nl) std::memcpy((void*)F.mvKeys.data(), kps_l, sizeof(orc_keypoint) * nl);
+    if (nr) std::memcpy((void*)F.mvKeysRight.data(), kps_r, sizeof(orc_keypoint) * nr);
+    F.mDescriptors = cv::Mat(nl, 32, CV_8UC1, (void*)desc_l, 32);
+    F.mDescriptorsRight = cv::Mat(nr, 32, CV_8UC1, (void*)desc_r, 32);
+    F.mvLevelSigma2.assign(level_sigma2, level_sigma2 + nlevels);
+    F.mRlr = mat_from(Rlr, 3, 3); F.mtlr = mat_from(tlr, 3, 1);
+    F.ComputeStereoFishEyeMatches();
+    int kept = 0;
+    for (int i = 0; i < nl; i++) {
+        left_to_right[i] = F.mvLeftToRightMatch[i];
+        depth[i] = F.mvDepth[i];
+        const cv::Mat& p = F.mvStereo3Dpoints[i];
+        for (int k = 0; k < 3; k++) p3d[3 * i + k] = p.empty() ? 0.f : p.at<float>(k);
+        kept += F.mvLeftToRightMatch[i] >= 0;
+    }
+    for (int i = 0; i < nr; i++) right_to_left[i] = F.mvRightToLeftMatch[i];
+    return kept;
 }
 
 /* ORBmatcher::SearchByProjection(CurrentFrame, LastFrame, th, bMono) (src/ORBmatcher.cc:2193-2419) on two frames given as arrays.

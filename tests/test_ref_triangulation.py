@@ -116,3 +116,39 @@ def test_search_for_triangulation_rig_equals_reference(cfg):
         assert nm == rnm and np.array_equal(m, rm), (cfg, coarse, ori)
         counts.append(nm)
     assert counts[2] > counts[1] > 20
+
+
+@pytest.mark.parametrize("seed,lap", [(800, (0, 511)), (801, (100, 400)), (802, (0, 511))])
+def test_fisheye_stereo_frame_equals_reference(seed, lap):
+    """Frame::ComputeStereoFishEyeMatches (src/Frame.cc:1119-1159) — the reference's own body, compiled (its BFMatcher::knnMatch is OpenCV's code:
+    the stand-in keeps, per query, the two smallest Hamming distances in ascending order, the lower train row first among equals, which the knn
+    goldens pin to cv2.BFMatcher) — against what the oracle composes for the same frame: knn-2 with `d0 < d1 * 0.7` in double over the rows
+    inside the lapping interval, TriangulateMatches per survivor, `depth > 0.0001f`.  Every output vector identical, depths and points to the bit."""
+    from orb_slam3_detailed_comments_kor_b200 import synth
+    fL, fR = synth.stereo_pair(seed, 512, 512)
+    params = (1500, 1.2, 8, 20, 7)
+    xl, xr = O.OracleExtractor(*params), O.OracleExtractor(*params)
+    ml, kl, dl = xl(fL, lap)
+    mr, kr, dr = xr(fR, lap)
+    cam1 = np.array([190.978, 190.973, 254.93, 256.90, 0.00348, 0.000715, -0.00205, 0.000203], np.float32)
+    cam2 = np.array([190.442, 190.434, 252.60, 254.92, 0.00340, 0.001766, -0.00266, 0.00033], np.float32)
+    if seed == 802:                                                       # the shim probe's rig: no distortion, a pure baseline
+        cam1 = cam2 = np.array([190, 190, 256, 256, 0, 0, 0, 0], np.float32)
+    Rlr, tlr = np.eye(3, dtype=np.float32), np.array([0.1, 0.0, 0.0], np.float32)
+    sig = (np.asarray(xl.scale_factors(), np.float32) ** 2).astype(np.float32)
+    l2r, r2l, depth, p3d, kept = R.fisheye_stereo(kl, dl, ml, kr, dr, mr, cam1, cam2, Rlr, tlr, sig)
+    knn = O.knn2_ratio(dl[ml:], dr[mr:], 0.7)
+    knn = knn[0] if isinstance(knn, tuple) else knn
+    want_l2r, want_r2l = np.full(len(kl), -1, np.int32), np.full(len(kr), -1, np.int32)
+    want_depth, want_p3d = np.full(len(kl), -1, np.float32), np.zeros((len(kl), 3), np.float32)
+    qi = np.nonzero(knn >= 0)[0]
+    if len(qi):
+        li, ri = qi + ml, knn[qi] + mr
+        d, p = O.kb8_triangulate_matches(cam1, cam2, Rlr, tlr, np.stack([kl["x"][li], kl["y"][li]], 1), np.stack([kr["x"][ri], kr["y"][ri]], 1),
+                                         sig[kl["octave"][li]], sig[kr["octave"][ri]])
+        for a, b, dd, pp in zip(li, ri, d, p):                            # in query order: a later query may overwrite mvRightToLeftMatch of the same right row
+            if dd > np.float32(0.0001):
+                want_l2r[a], want_r2l[b], want_depth[a], want_p3d[a] = b, a, dd, pp
+    assert np.array_equal(l2r, want_l2r) and np.array_equal(r2l, want_r2l)
+    assert np.array_equal(depth, want_depth) and np.array_equal(p3d, want_p3d)
+    assert kept == int((want_l2r >= 0).sum()) and (kept >= 3 or seed == 801)
