@@ -26,6 +26,7 @@
 #define SI_ROWS 48
 #define SI_CELLS (SI_COLS * SI_ROWS)
 #define SI_CACHE 1536
+#define SI_G 8          /* lanes that share one keypoint of F1 in a round */
 
 struct SiSmem {
     int cellEnd[SI_CELLS];       /* end of each cell's run in `sorted` */
@@ -174,18 +175,24 @@ __global__ void __launch_bounds__(SI_NT) k_search_for_initialization(const orbfe
         __syncthreads();
         if (tid == 0) s_minChanged = INT_MAX;
         __syncthreads();
+        /* SI_G lanes share a keypoint of F1: its window spans a dozen or more grid columns with very unequal numbers of keypoints, and with a
+         * thread per keypoint most lanes of a warp wait for its longest window.  Each lane takes every SI_G-th column; the reference's update
+         * rule (`dist < bestDist`: the old best becomes the second; `else if dist < bestDist2`) keeps the two smallest candidates in the order
+         * (distance, position in the walk), so a lane keeps two keys distance << 16 | position and the group merges them. */
         int myMin = INT_MAX;
-        for (int k = tid; k < nq; k += SI_NT) {
+        const int gl = tid & (SI_G - 1), leader = tid & 31 & ~(SI_G - 1);
+        const unsigned gmask = ((1u << SI_G) - 1u) << leader;
+        for (int k = tid / SI_G; k < nq; k += SI_NT / SI_G) {
             const int q = s.qList[k];
-            if (rounds > 0 && q <= firstDirty) { nx[q] = st[q]; continue; }
+            if (rounds > 0 && q <= firstDirty) { if (gl == 0) nx[q] = st[q]; continue; }
             const float x = prev[2 * q], y = prev[2 * q + 1];
-            int bestDist = INT_MAX, bestDist2 = INT_MAX, bestIdx2 = -1;
+            unsigned k1 = 0xFFFFFFFFu, k2 = 0xFFFFFFFFu;
             const float ax = x - g.min_x, ay = y - g.min_y;
             const int x0 = max(0, (int)floorf((ax - r) * g.inv_w)), x1 = min(SI_COLS - 1, (int)ceilf((ax + r) * g.inv_w));
             const int y0 = max(0, (int)floorf((ay - r) * g.inv_h)), y1 = min(SI_ROWS - 1, (int)ceilf((ay + r) * g.inv_h));
             if (x0 < SI_COLS && x1 >= 0 && y0 < SI_ROWS && y1 >= 0) {
                 const uint4 qa = __ldg(desc1 + 2 * q), qb = __ldg(desc1 + 2 * q + 1);
-                for (int ix = x0; ix <= x1; ix++) {
+                for (int ix = x0 + gl; ix <= x1; ix += SI_G) {
                     const int c0 = ix * SI_ROWS + y0, c1 = ix * SI_ROWS + y1;
                     const int beg = c0 ? s.cellEnd[c0 - 1] : 0, end = s.cellEnd[c1];
                     for (int j = beg; j < end; j++) {
@@ -200,15 +207,27 @@ __global__ void __launch_bounds__(SI_NT) k_search_for_initialization(const orbfe
                             held = (int)(st[qw] >> 16);
                         }
                         if (held <= dist) continue;
-                        if (dist < bestDist) { bestDist2 = bestDist; bestDist = dist; bestIdx2 = i2; }
-                        else if (dist < bestDist2) bestDist2 = dist;
+                        const unsigned key = ((unsigned)dist << 16) | (unsigned)j;
+                        if (key < k1) { k2 = k1; k1 = key; }
+                        else if (key < k2) k2 = key;
                     }
                 }
             }
-            uint32_t v = 0;
-            if (bestIdx2 >= 0 && bestDist <= thLow && (float)bestDist < __fmul_rn((float)bestDist2, nnratio)) v = ((uint32_t)bestDist << 16) | (uint32_t)(bestIdx2 + 1);
-            nx[q] = v;
-            if (v != st[q]) myMin = min(myMin, q);
+#pragma unroll
+            for (int o = SI_G >> 1; o; o >>= 1) {
+                const unsigned o1 = __shfl_xor_sync(gmask, k1, o), o2 = __shfl_xor_sync(gmask, k2, o);
+                const unsigned lo = min(k1, o1), hi = max(k1, o1);
+                k2 = min(hi, min(k2, o2));
+                k1 = lo;
+            }
+            if (gl == 0) {
+                const int bestDist = k1 == 0xFFFFFFFFu ? INT_MAX : (int)(k1 >> 16), bestDist2 = k2 == 0xFFFFFFFFu ? INT_MAX : (int)(k2 >> 16);
+                uint32_t v = 0;
+                if (k1 != 0xFFFFFFFFu && bestDist <= thLow && (float)bestDist < __fmul_rn((float)bestDist2, nnratio))
+                    v = ((uint32_t)bestDist << 16) | (uint32_t)(s.sorted[k1 & 0xFFFFu] + 1);
+                nx[q] = v;
+                if (v != st[q]) myMin = min(myMin, q);
+            }
         }
         if (myMin != INT_MAX) atomicMin(&s_minChanged, myMin);
         __syncthreads();
