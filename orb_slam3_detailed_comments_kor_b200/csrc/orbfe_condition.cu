@@ -3,9 +3,9 @@
  *   k_remap_linear   cv::remap(im, imRect, M1, M2, cv::INTER_LINEAR) with CV_32FC1 maps, BORDER_CONSTANT(0): the stereo
  *                    rectification of the example drivers (/root/reference/Examples/Stereo-Inertial/stereo_inertial_euroc.cc:201-202,
  *                    maps from cv::initUndistortRectifyMap(..., CV_32F, ...) at :150-151)
- *   k_to_gray        cv::cvtColor(im, gray, RGB2GRAY / BGR2GRAY / RGBA2GRAY / BGRA2GRAY) of Tracking::GrabImage*
+ *   k_to_gray4, k_to_gray   cv::cvtColor(im, gray, RGB2GRAY / BGR2GRAY / RGBA2GRAY / BGRA2GRAY) of Tracking::GrabImage*
  *                    (/root/reference/src/Tracking.cc:1303-1328)
- *   k_clahe_lut, k_clahe_apply   cv::createCLAHE(3.0, cv::Size(8, 8))->apply(im, im) of the TUM-VI drivers
+ *   k_clahe_lut, k_clahe_apply_band, k_clahe_apply   cv::createCLAHE(3.0, cv::Size(8, 8))->apply(im, im) of the TUM-VI drivers
  *                    (/root/reference/Examples/Stereo-Inertial/stereo_inertial_tum_vi.cc:128-138, Examples/Monocular/mono_tum_vi.cc)
  * Arithmetic (verified bit-exact against cv2 4.13.0, tests/golden/conditioning.npz):
  *   remap: sx = cvRound(mapx*32), ix = sx >> 5, fx = sx & 31 (same for y, ix/iy saturated to int16); weights
